@@ -1,0 +1,825 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h header; parity unpinned).
+//
+// Objectives, gradient quantisation, histograms, split search, leaf-wise learner (serial and simulated
+// data-parallel over S row shards) and the GBDT loop.  Restates upstream
+//   src/objective/{binary,regression,rank}_objective.hpp       
+//   src/treelearner/gradient_discretizer.cpp                   (A.6.4)
+//   src/io/dense_bin.hpp, src/io/dataset.cpp                   (A.5)
+//   src/treelearner/feature_histogram.hpp                      (A.7)
+//   src/treelearner/{serial,data_parallel}_tree_learner.cpp, data_partition.hpp, leaf_splits.hpp  (A.8)
+//   src/boosting/gbdt.cpp, gbdt_model_text.cpp                 (A.9, A.10)
+// Reference triggers: LGBM_BoosterCreate (lightgbm/.../TrainUtils.scala:16-29 ->
+// booster/LightGBMBooster.scala:241) and LGBM_BoosterUpdateOneIter (TrainUtils.scala:98-135 ->
+// LightGBMBooster.scala:355-365); collectives replace the socket learner set up by
+// LGBM_NetworkInit (NetworkManager.scala:195-218).
+#pragma once
+#include <algorithm>
+#include <numeric>
+
+#include "orc_dataset.h"
+#include "orc_tree.h"
+
+namespace orc {
+
+struct SplitInfo {
+  int feature = -1;            // inner feature index
+  int real_feature = -1;
+  uint32_t threshold = 0;
+  data_size_t left_count = 0, right_count = 0;
+  double left_output = 0.0, right_output = 0.0;
+  double gain = kMinScore;
+  double left_sum_gradient = 0.0, left_sum_hessian = 0.0, right_sum_gradient = 0.0, right_sum_hessian = 0.0;
+  int64_t left_int_g = 0, left_int_h = 0, right_int_g = 0, right_int_h = 0;
+  bool default_left = true;
+  void Reset() { *this = SplitInfo(); }
+  // upstream SplitInfo::operator> : larger gain wins; equal gain -> smaller feature index (-1 counts as +inf)
+  bool BetterThan(const SplitInfo& o) const {
+    int lf = real_feature == -1 ? INT32_MAX : real_feature;
+    int of = o.real_feature == -1 ? INT32_MAX : o.real_feature;
+    if (gain != o.gain) return gain > o.gain;
+    return lf < of;
+  }
+};
+
+struct SplitParams {
+  double l1, l2, max_delta_step, min_gain_to_split, min_sum_hessian;
+  int min_data_in_leaf;
+};
+
+inline double ThresholdL1(double s, double l1) {
+  double reg = std::max(0.0, std::fabs(s) - l1);
+  return Sign(s) * reg;
+}
+inline double LeafOutput(double g, double h, const SplitParams& p) {
+  double ret = (p.l1 > 0.0) ? -ThresholdL1(g, p.l1) / (h + p.l2) : -g / (h + p.l2);
+  if (p.max_delta_step > 0.0 && std::fabs(ret) > p.max_delta_step) ret = Sign(ret) * p.max_delta_step;
+  return ret;
+}
+inline double LeafGainGivenOutput(double g, double h, const SplitParams& p, double out) {
+  double sg = (p.l1 > 0.0) ? ThresholdL1(g, p.l1) : g;
+  return -(2.0 * sg * out + (h + p.l2) * out * out);
+}
+inline double LeafGain(double g, double h, const SplitParams& p) {
+  if (p.max_delta_step <= 0.0) {
+    double sg = (p.l1 > 0.0) ? ThresholdL1(g, p.l1) : g;
+    return (sg * sg) / (h + p.l2);
+  }
+  return LeafGainGivenOutput(g, h, p, LeafOutput(g, h, p));
+}
+inline double SplitGain(double lg, double lh, double rg, double rh, const SplitParams& p) {
+  return LeafGain(lg, lh, p) + LeafGain(rg, rh, p);
+}
+
+// Float-histogram threshold search for one numerical feature (FindBestThresholdSequentially, both directions).
+// hist: num_bin (g,h) pairs in logical bin order.  Returns is_splittable.
+inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, double sum_gradient, double sum_hessian_in,
+                                   data_size_t num_data, const SplitParams& p, SplitInfo* out) {
+  out->default_left = true;
+  out->gain = kMinScore;
+  const double sum_hessian = sum_hessian_in + 2 * kEpsilon;
+  const double gain_shift = LeafGain(sum_gradient, sum_hessian, p);
+  const double min_gain_shift = gain_shift + p.min_gain_to_split;
+  const int num_bin = m.num_bin;
+  const double cnt_factor = num_data / sum_hessian;
+  bool splittable = false;
+  auto scan = [&](bool reverse, bool na_as_missing) {
+    double best_lg = std::numeric_limits<double>::quiet_NaN(), best_lh = best_lg;
+    double best_gain = kMinScore;
+    data_size_t best_left_count = 0;
+    uint32_t best_threshold = static_cast<uint32_t>(num_bin);
+    if (reverse) {
+      double rg = 0.0, rh = kEpsilon;
+      data_size_t rc = 0;
+      for (int b = num_bin - 1 - (na_as_missing ? 1 : 0); b >= 1; --b) {
+        double g = hist[2 * b], h = hist[2 * b + 1];
+        rg += g; rh += h; rc += RoundInt(h * cnt_factor);
+        if (rc < p.min_data_in_leaf || rh < p.min_sum_hessian) continue;
+        data_size_t lc = num_data - rc;
+        if (lc < p.min_data_in_leaf) break;
+        double lh = sum_hessian - rh;
+        if (lh < p.min_sum_hessian) break;
+        double lg = sum_gradient - rg;
+        double gain = SplitGain(lg, lh, rg, rh, p);
+        if (gain <= min_gain_shift) continue;
+        splittable = true;
+        if (gain > best_gain) {
+          best_left_count = lc; best_lg = lg; best_lh = lh;
+          best_threshold = static_cast<uint32_t>(b - 1);
+          best_gain = gain;
+        }
+      }
+    } else {
+      double lg = 0.0, lh = kEpsilon;
+      data_size_t lc = 0;
+      for (int b = 0; b <= num_bin - 2; ++b) {
+        double g = hist[2 * b], h = hist[2 * b + 1];
+        lg += g; lh += h; lc += RoundInt(h * cnt_factor);
+        if (lc < p.min_data_in_leaf || lh < p.min_sum_hessian) continue;
+        data_size_t rc = num_data - lc;
+        if (rc < p.min_data_in_leaf) break;
+        double rh = sum_hessian - lh;
+        if (rh < p.min_sum_hessian) break;
+        double rg = sum_gradient - lg;
+        double gain = SplitGain(lg, lh, rg, rh, p);
+        if (gain <= min_gain_shift) continue;
+        splittable = true;
+        if (gain > best_gain) {
+          best_left_count = lc; best_lg = lg; best_lh = lh;
+          best_threshold = static_cast<uint32_t>(b);
+          best_gain = gain;
+        }
+      }
+    }
+    if (splittable && best_gain > out->gain + min_gain_shift) {
+      out->threshold = best_threshold;
+      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_count = best_left_count;
+      out->left_sum_gradient = best_lg;
+      out->left_sum_hessian = best_lh - kEpsilon;
+      out->right_output = LeafOutput(sum_gradient - best_lg, sum_hessian - best_lh, p);
+      out->right_count = num_data - best_left_count;
+      out->right_sum_gradient = sum_gradient - best_lg;
+      out->right_sum_hessian = sum_hessian - best_lh - kEpsilon;
+      out->gain = best_gain - min_gain_shift;
+      out->default_left = reverse;
+    }
+  };
+  if (num_bin > 2 && m.missing_type == MISSING_NAN) {
+    scan(true, true);
+    scan(false, true);
+  } else {
+    scan(true, false);
+    if (m.missing_type == MISSING_NAN) out->default_left = false;
+  }
+  return splittable;
+}
+
+// Integer-histogram threshold search (FindBestThresholdSequentiallyInt): prefix sums are exact integers, gains are
+// evaluated on int_sum * scale.
+inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_t int_sum_g, int64_t int_sum_h,
+                                 double grad_scale, double hess_scale, data_size_t num_data, const SplitParams& p,
+                                 SplitInfo* out) {
+  out->default_left = true;
+  out->gain = kMinScore;
+  const double sum_gradient = static_cast<double>(int_sum_g) * grad_scale;
+  const double sum_hessian = static_cast<double>(int_sum_h) * hess_scale;
+  const double gain_shift = LeafGain(sum_gradient, sum_hessian, p);
+  const double min_gain_shift = gain_shift + p.min_gain_to_split;
+  const int num_bin = m.num_bin;
+  if (int_sum_h <= 0) return false;   // guard (upstream would divide by zero)
+  const double cnt_factor = static_cast<double>(num_data) / static_cast<double>(int_sum_h);
+  bool splittable = false;
+  auto scan = [&](bool reverse, bool na_as_missing) {
+    int64_t best_lg = 0, best_lh = 0;
+    double best_gain = kMinScore;
+    uint32_t best_threshold = static_cast<uint32_t>(num_bin);
+    if (reverse) {
+      int64_t rg = 0, rh = 0;
+      for (int b = num_bin - 1 - (na_as_missing ? 1 : 0); b >= 1; --b) {
+        rg += hist[2 * b]; rh += hist[2 * b + 1];
+        data_size_t rc = RoundInt(static_cast<double>(rh) * cnt_factor);
+        double srh = static_cast<double>(rh) * hess_scale;
+        if (rc < p.min_data_in_leaf || srh < p.min_sum_hessian) continue;
+        data_size_t lc = num_data - rc;
+        if (lc < p.min_data_in_leaf) break;
+        int64_t lg = int_sum_g - rg, lh = int_sum_h - rh;
+        double slh = static_cast<double>(lh) * hess_scale;
+        if (slh < p.min_sum_hessian) break;
+        double srg = static_cast<double>(rg) * grad_scale, slg = static_cast<double>(lg) * grad_scale;
+        double gain = SplitGain(slg, slh, srg, srh, p);
+        if (gain <= min_gain_shift) continue;
+        splittable = true;
+        if (gain > best_gain) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b - 1); best_gain = gain; }
+      }
+    } else {
+      int64_t lg = 0, lh = 0;
+      for (int b = 0; b <= num_bin - 2; ++b) {
+        lg += hist[2 * b]; lh += hist[2 * b + 1];
+        data_size_t lc = RoundInt(static_cast<double>(lh) * cnt_factor);
+        double slh = static_cast<double>(lh) * hess_scale;
+        if (lc < p.min_data_in_leaf || slh < p.min_sum_hessian) continue;
+        data_size_t rc = num_data - lc;
+        if (rc < p.min_data_in_leaf) break;
+        int64_t rg = int_sum_g - lg, rh = int_sum_h - lh;
+        double srh = static_cast<double>(rh) * hess_scale;
+        if (srh < p.min_sum_hessian) break;
+        double srg = static_cast<double>(rg) * grad_scale, slg = static_cast<double>(lg) * grad_scale;
+        double gain = SplitGain(slg, slh, srg, srh, p);
+        if (gain <= min_gain_shift) continue;
+        splittable = true;
+        if (gain > best_gain) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b); best_gain = gain; }
+      }
+    }
+    if (splittable && best_gain > out->gain + min_gain_shift) {
+      int64_t rg = int_sum_g - best_lg, rh = int_sum_h - best_lh;
+      double blg = static_cast<double>(best_lg) * grad_scale, blh = static_cast<double>(best_lh) * hess_scale;
+      double brg = static_cast<double>(rg) * grad_scale, brh = static_cast<double>(rh) * hess_scale;
+      out->threshold = best_threshold;
+      out->left_output = LeafOutput(blg, blh, p);
+      out->left_count = RoundInt(static_cast<double>(best_lh) * cnt_factor);
+      out->left_sum_gradient = blg; out->left_sum_hessian = blh;
+      out->left_int_g = best_lg; out->left_int_h = best_lh;
+      out->right_output = LeafOutput(brg, brh, p);
+      out->right_count = RoundInt(static_cast<double>(rh) * cnt_factor);
+      out->right_sum_gradient = brg; out->right_sum_hessian = brh;
+      out->right_int_g = rg; out->right_int_h = rh;
+      out->gain = best_gain - min_gain_shift;
+      out->default_left = reverse;
+    }
+  };
+  if (num_bin > 2 && m.missing_type == MISSING_NAN) {
+    scan(true, true);
+    scan(false, true);
+  } else {
+    scan(true, false);
+    if (m.missing_type == MISSING_NAN) out->default_left = false;
+  }
+  return splittable;
+}
+
+struct Shard {
+  const Dataset* ds = nullptr;
+  int64_t row_offset = 0;                 // global row id of local row 0 (for the stochastic-rounding stream)
+  std::vector<double> score;
+  std::vector<score_t> grad, hess;
+  std::vector<int8_t> qg, qh;             // quantized gradient / hessian
+  std::vector<data_size_t> indices, tmp_left, tmp_right;
+  std::vector<data_size_t> leaf_begin, leaf_count;
+};
+
+class Booster {
+ public:
+  Config cfg;
+  std::vector<Shard> shards;
+  int S = 1, F = 0, B = 1;
+  bool dp = false;                         // data-parallel semantics (global estimated counts) when S > 1
+  std::vector<std::unique_ptr<Tree>> models;
+  int iter = 0;
+  // objective state
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK } obj = OBJ_L2;
+  bool need_train = true;
+  double label_weights[2] = {1.0, 1.0};
+  bool has_weights = false;
+  std::vector<double> label_gain, discount, sigmoid_table;
+  std::vector<std::vector<double>> inverse_max_dcgs;   // per shard per query
+  double min_sigmoid_input = -50, max_sigmoid_input = 50, sigmoid_table_idx_factor = 1;
+  // learner state
+  SplitParams sp;
+  double grad_scale = 1.0, hess_scale = 1.0;
+  struct Leaf {
+    double sum_g = 0, sum_h = 0; int64_t int_g = 0, int_h = 0;
+    data_size_t count = 0;               // count used by the split finder (serial: true; dp: global estimate)
+    SplitInfo best;
+    std::vector<char> splittable;
+  };
+  std::vector<Leaf> leaves;
+  std::vector<std::vector<double>> hist_f;   // per leaf: F*B*2 doubles
+  std::vector<std::vector<int64_t>> hist_i;  // per leaf: F*B*2 int64
+  int64_t total_rows = 0;
+
+  Booster(const std::vector<const Dataset*>& ds, const char* params) {
+    cfg = ds[0]->config;     // dataset-time params (max_bin ...) first, booster string overrides
+    cfg.Set(params ? params : "");
+    S = static_cast<int>(ds.size());
+    dp = S > 1;
+    F = ds[0]->num_features();
+    B = ds[0]->max_num_bin;
+    shards.resize(S);
+    int64_t off = 0;
+    for (int s = 0; s < S; ++s) {
+      shards[s].ds = ds[s];
+      shards[s].row_offset = off;
+      off += ds[s]->num_data;
+      int64_t n = ds[s]->num_data;
+      shards[s].score.assign(n, 0.0);
+      shards[s].grad.assign(n, 0.0f);
+      shards[s].hess.assign(n, 0.0f);
+      if (cfg.use_quantized_grad) { shards[s].qg.assign(n, 0); shards[s].qh.assign(n, 0); }
+      shards[s].indices.resize(n); shards[s].tmp_left.resize(n); shards[s].tmp_right.resize(n);
+      shards[s].leaf_begin.assign(cfg.num_leaves, 0); shards[s].leaf_count.assign(cfg.num_leaves, 0);
+      if (ds[s]->has_init_score) for (int64_t i = 0; i < n; ++i) shards[s].score[i] = ds[s]->init_score[i];
+    }
+    total_rows = off;
+    has_weights = ds[0]->has_weight;
+    sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf};
+    if (cfg.boosting != "gbdt") throw std::runtime_error("oracle: only boosting=gbdt is restated");
+    if (cfg.zero_as_missing) throw std::runtime_error("oracle: zero_as_missing is not restated");
+    InitObjective();
+  }
+
+  // ---------------------------------------------------------------- objectives
+  void InitObjective() {
+    if (cfg.objective == "binary") {
+      obj = OBJ_BINARY;
+      int64_t pos = 0, neg = 0;
+      for (auto& sh : shards) for (float l : sh.ds->label) { if (l > 0) ++pos; else ++neg; }   // global (summed over machines)
+      need_train = !(pos == 0 || neg == 0);
+      label_weights[0] = label_weights[1] = 1.0;
+      if (cfg.is_unbalance && pos > 0 && neg > 0) {
+        if (pos > neg) { label_weights[1] = 1.0; label_weights[0] = static_cast<double>(pos) / neg; }
+        else { label_weights[1] = static_cast<double>(neg) / pos; label_weights[0] = 1.0; }
+      }
+      label_weights[1] *= cfg.scale_pos_weight;
+    } else if (cfg.objective == "regression") {
+      obj = OBJ_L2;
+    } else if (cfg.objective == "lambdarank") {
+      obj = OBJ_LAMBDARANK;
+      label_gain = cfg.label_gain;
+      if (label_gain.empty()) { for (int i = 0; i < 31; ++i) label_gain.push_back(static_cast<double>((1LL << i) - 1)); }
+      discount.resize(10000);
+      for (int i = 0; i < 10000; ++i) discount[i] = 1.0 / std::log2(2.0 + i);
+      inverse_max_dcgs.resize(S);
+      for (int s = 0; s < S; ++s) {
+        const Dataset* d = shards[s].ds;
+        if (d->query_boundaries.empty()) throw std::runtime_error("lambdarank requires query information");
+        int nq = static_cast<int>(d->query_boundaries.size()) - 1;
+        inverse_max_dcgs[s].resize(nq);
+        for (int q = 0; q < nq; ++q) {
+          int b = d->query_boundaries[q], cnt = d->query_boundaries[q + 1] - b;
+          double v = MaxDCGAtK(cfg.lambdarank_truncation_level, d->label.data() + b, cnt);
+          if (v > 0.0) v = 1.0f / v;
+          inverse_max_dcgs[s][q] = v;
+        }
+      }
+      // sigmoid table (ConstructSigmoidTable)
+      const size_t bins = 1024 * 1024;
+      min_sigmoid_input = -50.0 / cfg.sigmoid / 2;
+      max_sigmoid_input = -min_sigmoid_input;
+      sigmoid_table.resize(bins);
+      sigmoid_table_idx_factor = bins / (max_sigmoid_input - min_sigmoid_input);
+      for (size_t i = 0; i < bins; ++i) {
+        const double sc = i / sigmoid_table_idx_factor + min_sigmoid_input;
+        sigmoid_table[i] = 1.0f / (1.0f + std::exp(sc * cfg.sigmoid));
+      }
+    } else {
+      throw std::runtime_error("oracle: objective not restated: " + cfg.objective);
+    }
+  }
+
+  double MaxDCGAtK(int k, const label_t* label, int num) const {
+    double ret = 0.0;
+    std::vector<int> label_cnt(label_gain.size(), 0);
+    for (int i = 0; i < num; ++i) ++label_cnt[static_cast<int>(label[i])];
+    int top_label = static_cast<int>(label_gain.size()) - 1;
+    if (k > num) k = num;
+    for (int j = 0; j < k; ++j) {
+      while (top_label > 0 && label_cnt[top_label] <= 0) top_label -= 1;
+      if (top_label < 0) break;
+      ret += discount[j] * label_gain[top_label];
+      label_cnt[top_label] -= 1;
+    }
+    return ret;
+  }
+
+  double GetSigmoid(double score) const {
+    if (score <= min_sigmoid_input) return sigmoid_table[0];
+    if (score >= max_sigmoid_input) return sigmoid_table[sigmoid_table.size() - 1];
+    return sigmoid_table[static_cast<size_t>((score - min_sigmoid_input) * sigmoid_table_idx_factor)];
+  }
+
+  double BoostFromScore() const {
+    double suml = 0.0, sumw = 0.0;
+    if (obj == OBJ_BINARY) {
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        if (has_weights) { for (int64_t i = 0; i < d->num_data; ++i) { suml += (d->label[i] > 0) * d->weight[i]; sumw += d->weight[i]; } }
+        else { sumw += static_cast<double>(d->num_data); for (int64_t i = 0; i < d->num_data; ++i) suml += (d->label[i] > 0); }
+      }
+      double pavg = suml / sumw;
+      pavg = std::min(pavg, 1.0 - kEpsilon);
+      pavg = std::max<double>(pavg, kEpsilon);
+      return std::log(pavg / (1.0f - pavg)) / cfg.sigmoid;
+    }
+    if (obj == OBJ_L2) {
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        if (has_weights) { for (int64_t i = 0; i < d->num_data; ++i) { suml += d->label[i] * d->weight[i]; sumw += d->weight[i]; } }
+        else { sumw += static_cast<double>(d->num_data); for (int64_t i = 0; i < d->num_data; ++i) suml += d->label[i]; }
+      }
+      return suml / sumw;
+    }
+    return 0.0;
+  }
+
+  void GetGradients() {
+    for (int s = 0; s < S; ++s) {
+      Shard& sh = shards[s];
+      const Dataset* d = sh.ds;
+      const int64_t n = d->num_data;
+      if (obj == OBJ_BINARY) {
+        if (!need_train) continue;
+        const double sig = cfg.sigmoid;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+          const int is_pos = d->label[i] > 0;
+          const int label = is_pos ? 1 : -1;
+          const double lw = label_weights[is_pos];
+          const double response = -label * sig / (1.0f + SoftExp(label * sig * sh.score[i]));
+          const double abs_response = std::fabs(response);
+          if (!has_weights) {
+            sh.grad[i] = static_cast<score_t>(response * lw);
+            sh.hess[i] = static_cast<score_t>(abs_response * (sig - abs_response) * lw);
+          } else {
+            sh.grad[i] = static_cast<score_t>(response * lw * d->weight[i]);
+            sh.hess[i] = static_cast<score_t>(abs_response * (sig - abs_response) * lw * d->weight[i]);
+          }
+        }
+      } else if (obj == OBJ_L2) {
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+          if (!has_weights) {
+            sh.grad[i] = static_cast<score_t>(sh.score[i] - d->label[i]);
+            sh.hess[i] = 1.0f;
+          } else {
+            sh.grad[i] = static_cast<score_t>(static_cast<score_t>(sh.score[i] - d->label[i]) * d->weight[i]);
+            sh.hess[i] = static_cast<score_t>(d->weight[i]);
+          }
+        }
+      } else {
+        const int nq = static_cast<int>(d->query_boundaries.size()) - 1;
+#pragma omp parallel for schedule(guided)
+        for (int q = 0; q < nq; ++q) {
+          const int start = d->query_boundaries[q];
+          const int cnt = d->query_boundaries[q + 1] - start;
+          LambdarankOneQuery(inverse_max_dcgs[s][q], cnt, d->label.data() + start, sh.score.data() + start,
+                             sh.grad.data() + start, sh.hess.data() + start);
+          if (has_weights) {
+            for (int j = 0; j < cnt; ++j) {
+              sh.grad[start + j] = static_cast<score_t>(sh.grad[start + j] * d->weight[start + j]);
+              sh.hess[start + j] = static_cast<score_t>(sh.hess[start + j] * d->weight[start + j]);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  void LambdarankOneQuery(double inverse_max_dcg, int cnt, const label_t* label, const double* score, score_t* lambdas,
+                          score_t* hessians) const {
+    for (int i = 0; i < cnt; ++i) { lambdas[i] = 0.0f; hessians[i] = 0.0f; }
+    std::vector<int> sorted_idx(cnt);
+    for (int i = 0; i < cnt; ++i) sorted_idx[i] = i;
+    std::stable_sort(sorted_idx.begin(), sorted_idx.end(), [score](int a, int b) { return score[a] > score[b]; });
+    const double best_score = score[sorted_idx[0]];
+    int worst_idx = cnt - 1;
+    if (worst_idx > 0 && score[sorted_idx[worst_idx]] == kMinScore) worst_idx -= 1;
+    const double worst_score = score[sorted_idx[worst_idx]];
+    double sum_lambdas = 0.0;
+    const double sig = cfg.sigmoid;
+    for (int i = 0; i < cnt - 1 && i < cfg.lambdarank_truncation_level; ++i) {
+      if (score[sorted_idx[i]] == kMinScore) continue;
+      for (int j = i + 1; j < cnt; ++j) {
+        if (score[sorted_idx[j]] == kMinScore) continue;
+        if (label[sorted_idx[i]] == label[sorted_idx[j]]) continue;
+        int high_rank, low_rank;
+        if (label[sorted_idx[i]] > label[sorted_idx[j]]) { high_rank = i; low_rank = j; } else { high_rank = j; low_rank = i; }
+        const int high = sorted_idx[high_rank];
+        const int high_label = static_cast<int>(label[high]);
+        const double high_score = score[high];
+        const double high_label_gain = label_gain[high_label];
+        const double high_discount = discount[high_rank];
+        const int low = sorted_idx[low_rank];
+        const int low_label = static_cast<int>(label[low]);
+        const double low_score = score[low];
+        const double low_label_gain = label_gain[low_label];
+        const double low_discount = discount[low_rank];
+        const double delta_score = high_score - low_score;
+        const double dcg_gap = high_label_gain - low_label_gain;
+        const double paired_discount = std::fabs(high_discount - low_discount);
+        double delta_pair_NDCG = dcg_gap * paired_discount * inverse_max_dcg;
+        if (cfg.lambdarank_norm && best_score != worst_score) delta_pair_NDCG /= (0.01f + std::fabs(delta_score));
+        double p_lambda = GetSigmoid(delta_score);
+        double p_hessian = p_lambda * (1.0f - p_lambda);
+        p_lambda *= -sig * delta_pair_NDCG;
+        p_hessian *= sig * sig * delta_pair_NDCG;
+        lambdas[low] -= static_cast<score_t>(p_lambda);
+        hessians[low] += static_cast<score_t>(p_hessian);
+        lambdas[high] += static_cast<score_t>(p_lambda);
+        hessians[high] += static_cast<score_t>(p_hessian);
+        sum_lambdas -= 2 * p_lambda;
+      }
+    }
+    if (cfg.lambdarank_norm && sum_lambdas > 0) {
+      double norm_factor = SoftLog2(1 + sum_lambdas) / sum_lambdas;
+      for (int i = 0; i < cnt; ++i) {
+        lambdas[i] = static_cast<score_t>(lambdas[i] * norm_factor);
+        hessians[i] = static_cast<score_t>(hessians[i] * norm_factor);
+      }
+    }
+  }
+
+  // ---------------------------------------------------------------- gradient quantisation (A.6.4)
+  void Discretize() {
+    double max_g = 0.0, max_h = 0.0;
+    bool first = true;
+    for (auto& sh : shards) {
+      for (size_t i = 0; i < sh.grad.size(); ++i) {
+        double ag = std::fabs(sh.grad[i]), ah = std::fabs(sh.hess[i]);
+        if (first) { max_g = ag; max_h = ah; first = false; }
+        if (ag > max_g) max_g = ag;
+        if (ah > max_h) max_h = ah;
+      }
+    }
+    const bool const_hess = (obj == OBJ_L2 && !has_weights);
+    grad_scale = max_g / static_cast<double>(cfg.num_grad_quant_bins / 2);
+    hess_scale = const_hess ? max_h : max_h / static_cast<double>(cfg.num_grad_quant_bins);
+    const double inv_g = 1.0f / grad_scale, inv_h = 1.0f / hess_scale;
+    for (auto& sh : shards) {
+      const int64_t n = static_cast<int64_t>(sh.grad.size());
+#pragma omp parallel for schedule(static)
+      for (int64_t i = 0; i < n; ++i) {
+        const score_t g = sh.grad[i];
+        if (cfg.stochastic_rounding) {
+          const uint32_t row = static_cast<uint32_t>(sh.row_offset + i);
+          const float rg = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter), row, 0);
+          const float rh = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter), row, 1);
+          sh.qg[i] = g >= 0.0f ? static_cast<int8_t>(g * inv_g + rg) : static_cast<int8_t>(g * inv_g - rg);
+          sh.qh[i] = static_cast<int8_t>(sh.hess[i] * inv_h + rh);
+        } else {
+          sh.qg[i] = g >= 0.0f ? static_cast<int8_t>(g * inv_g + 0.5f) : static_cast<int8_t>(g * inv_g - 0.5f);
+          sh.qh[i] = static_cast<int8_t>(sh.hess[i] * inv_h + 0.5f);
+        }
+      }
+    }
+  }
+
+  // ---------------------------------------------------------------- histograms (A.5)
+  void ConstructHistogram(int leaf, const std::vector<char>& used) {
+    const bool q = cfg.use_quantized_grad;
+    const size_t sz = static_cast<size_t>(F) * B * 2;
+    if (q) hist_i[leaf].assign(sz, 0); else hist_f[leaf].assign(sz, 0.0);
+    for (int s = 0; s < S; ++s) {
+      Shard& sh = shards[s];
+      const Dataset* d = sh.ds;
+      const data_size_t b = sh.leaf_begin[leaf], n = sh.leaf_count[leaf];
+      const data_size_t* idx = sh.indices.data() + b;
+      // local histogram per machine, then summed in rank order (the socket / NCCL reduce)
+      std::vector<double> lf; std::vector<int64_t> li;
+      if (q) li.assign(sz, 0); else lf.assign(sz, 0.0);
+#pragma omp parallel for schedule(dynamic)
+      for (int f = 0; f < F; ++f) {
+        if (!used[f]) continue;
+        const size_t col = static_cast<size_t>(f) * d->num_data;
+        if (q) {
+          int64_t* h = li.data() + static_cast<size_t>(f) * B * 2;
+          if (d->wide) { for (data_size_t i = 0; i < n; ++i) { uint32_t bin = d->bins16[col + idx[i]]; h[2 * bin] += sh.qg[idx[i]]; h[2 * bin + 1] += sh.qh[idx[i]]; } }
+          else { for (data_size_t i = 0; i < n; ++i) { uint32_t bin = d->bins8[col + idx[i]]; h[2 * bin] += sh.qg[idx[i]]; h[2 * bin + 1] += sh.qh[idx[i]]; } }
+        } else {
+          double* h = lf.data() + static_cast<size_t>(f) * B * 2;
+          if (d->wide) { for (data_size_t i = 0; i < n; ++i) { uint32_t bin = d->bins16[col + idx[i]]; h[2 * bin] += sh.grad[idx[i]]; h[2 * bin + 1] += sh.hess[idx[i]]; } }
+          else { for (data_size_t i = 0; i < n; ++i) { uint32_t bin = d->bins8[col + idx[i]]; h[2 * bin] += sh.grad[idx[i]]; h[2 * bin + 1] += sh.hess[idx[i]]; } }
+        }
+      }
+      if (q) { for (size_t k = 0; k < sz; ++k) hist_i[leaf][k] += li[k]; }
+      else if (S == 1) { hist_f[leaf].swap(lf); }
+      else { for (size_t k = 0; k < sz; ++k) hist_f[leaf][k] += lf[k]; }
+    }
+  }
+
+  void FindBestForLeaf(int leaf, const std::vector<char>& used) {
+    Leaf& L = leaves[leaf];
+    std::vector<SplitInfo> per_feature(F);
+    std::vector<char> spl(F, 0);
+#pragma omp parallel for schedule(dynamic)
+    for (int f = 0; f < F; ++f) {
+      if (!used[f]) continue;
+      const BinMapper& m = shards[0].ds->inner_mapper(f);
+      SplitInfo si;
+      bool ok;
+      if (cfg.use_quantized_grad) {
+        ok = FindBestThresholdInt(hist_i[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.int_g, L.int_h, grad_scale,
+                                  hess_scale, L.count, sp, &si);
+      } else {
+        ok = FindBestThresholdFloat(hist_f[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, L.count, sp, &si);
+      }
+      si.feature = f;
+      si.real_feature = shards[0].ds->used_features[f];
+      per_feature[f] = si;
+      spl[f] = ok;
+    }
+    SplitInfo best;
+    for (int f = 0; f < F; ++f) {
+      if (!used[f]) { L.splittable[f] = 0; continue; }
+      L.splittable[f] = spl[f];
+      if (per_feature[f].BetterThan(best)) best = per_feature[f];
+    }
+    L.best = best;
+  }
+
+  // ---------------------------------------------------------------- tree learner (A.8)
+  std::unique_ptr<Tree> TrainTree() {
+    const int NL = cfg.num_leaves;
+    const bool q = cfg.use_quantized_grad;
+    if (q) Discretize();
+    leaves.assign(NL, Leaf());
+    for (auto& L : leaves) L.splittable.assign(F, 1);
+    if (q) hist_i.resize(NL); else hist_f.resize(NL);
+    for (auto& sh : shards) {
+      std::iota(sh.indices.begin(), sh.indices.end(), 0);
+      std::fill(sh.leaf_begin.begin(), sh.leaf_begin.end(), 0);
+      std::fill(sh.leaf_count.begin(), sh.leaf_count.end(), 0);
+      sh.leaf_count[0] = static_cast<data_size_t>(sh.ds->num_data);
+    }
+    // root sums
+    Leaf& root = leaves[0];
+    root.count = static_cast<data_size_t>(total_rows);
+    if (q) {
+      for (auto& sh : shards) for (size_t i = 0; i < sh.qg.size(); ++i) { root.int_g += sh.qg[i]; root.int_h += sh.qh[i]; }
+      root.sum_g = static_cast<double>(root.int_g) * grad_scale;
+      root.sum_h = static_cast<double>(root.int_h) * hess_scale;
+    } else {
+      for (auto& sh : shards) {
+        double sg = 0.0, shh = 0.0;
+        for (size_t i = 0; i < sh.grad.size(); ++i) { sg += sh.grad[i]; shh += sh.hess[i]; }
+        root.sum_g += sg; root.sum_h += shh;
+      }
+    }
+    std::unique_ptr<Tree> tree(new Tree(NL));
+    int left_leaf = 0, right_leaf = -1;
+    for (int split = 0; split < NL - 1; ++split) {
+      // BeforeFindBestSplit
+      bool go = true;
+      if (cfg.max_depth > 0 && tree->leaf_depth[left_leaf] >= cfg.max_depth) {
+        leaves[left_leaf].best.gain = kMinScore;
+        if (right_leaf >= 0) leaves[right_leaf].best.gain = kMinScore;
+        go = false;
+      }
+      if (go) {
+        data_size_t nl = leaves[left_leaf].count;
+        data_size_t nr = right_leaf >= 0 ? leaves[right_leaf].count : 0;
+        if (nr < cfg.min_data_in_leaf * 2 && nl < cfg.min_data_in_leaf * 2) {
+          leaves[left_leaf].best.gain = kMinScore;
+          if (right_leaf >= 0) leaves[right_leaf].best.gain = kMinScore;
+          go = false;
+        }
+        if (go) {
+          if (right_leaf < 0) {
+            std::vector<char> used(F, 1);
+            ConstructHistogram(0, used);
+            FindBestForLeaf(0, used);
+          } else {
+            int smaller = nl < nr ? left_leaf : right_leaf;
+            int larger = nl < nr ? right_leaf : left_leaf;
+            // the parent's histogram lives in slot left_leaf; features unsplittable at the parent stay so in both children
+            std::vector<char> used(F, 1);
+            for (int f = 0; f < F; ++f) used[f] = leaves[left_leaf].splittable[f];
+            if (q) { if (larger != left_leaf) hist_i[larger].swap(hist_i[left_leaf]); }
+            else { if (larger != left_leaf) hist_f[larger].swap(hist_f[left_leaf]); }
+            ConstructHistogram(smaller, used);
+            const size_t sz = static_cast<size_t>(F) * B * 2;
+            if (q) { for (size_t k = 0; k < sz; ++k) hist_i[larger][k] -= hist_i[smaller][k]; }
+            else { for (size_t k = 0; k < sz; ++k) hist_f[larger][k] -= hist_f[smaller][k]; }
+            FindBestForLeaf(smaller, used);
+            FindBestForLeaf(larger, used);
+          }
+        }
+      }
+      // leaf with max gain: (gain desc, feature asc, leaf asc)
+      int best_leaf = 0;
+      for (int l = 1; l < tree->num_leaves; ++l) if (leaves[l].best.BetterThan(leaves[best_leaf].best)) best_leaf = l;
+      const SplitInfo bs = leaves[best_leaf].best;
+      if (bs.gain <= 0.0) break;
+      Split(tree.get(), best_leaf, bs, &left_leaf, &right_leaf);
+    }
+    return tree;
+  }
+
+  void Split(Tree* tree, int best_leaf, SplitInfo bs, int* left_leaf, int* right_leaf) {
+    const Dataset* d0 = shards[0].ds;
+    const BinMapper& m = d0->inner_mapper(bs.feature);
+    *left_leaf = best_leaf;
+    const int next_leaf = tree->num_leaves;
+    // DataPartition::Split on every machine (stable)
+    data_size_t tot_left = 0, tot_right = 0;
+    for (auto& sh : shards) {
+      const Dataset* d = sh.ds;
+      const data_size_t b = sh.leaf_begin[best_leaf], n = sh.leaf_count[best_leaf];
+      data_size_t nl = 0, nr = 0;
+      const uint32_t nan_bin = static_cast<uint32_t>(m.num_bin - 1);
+      for (data_size_t i = 0; i < n; ++i) {
+        const data_size_t r = sh.indices[b + i];
+        const uint32_t bin = d->bin_at(bs.feature, r);
+        bool go_left;
+        if (m.missing_type == MISSING_NAN && bin == nan_bin) go_left = bs.default_left;
+        else go_left = bin <= bs.threshold;
+        if (go_left) sh.tmp_left[nl++] = r; else sh.tmp_right[nr++] = r;
+      }
+      std::copy(sh.tmp_left.begin(), sh.tmp_left.begin() + nl, sh.indices.begin() + b);
+      std::copy(sh.tmp_right.begin(), sh.tmp_right.begin() + nr, sh.indices.begin() + b + nl);
+      sh.leaf_count[best_leaf] = nl;
+      sh.leaf_begin[next_leaf] = b + nl;
+      sh.leaf_count[next_leaf] = nr;
+      tot_left += nl; tot_right += nr;
+    }
+    if (!dp) { bs.left_count = tot_left; bs.right_count = tot_right; }   // serial learner: true counts (update_cnt)
+    *right_leaf = tree->Split(best_leaf, bs.feature, bs.real_feature, bs.threshold, m.bin_upper_bound[bs.threshold],
+                              bs.left_output, bs.right_output, bs.left_count, bs.right_count, bs.left_sum_hessian,
+                              bs.right_sum_hessian, static_cast<float>(bs.gain), m.missing_type, bs.default_left);
+    std::vector<char> parent_spl = leaves[best_leaf].splittable;
+    Leaf& L = leaves[*left_leaf];
+    Leaf& R = leaves[*right_leaf];
+    L.sum_g = bs.left_sum_gradient; L.sum_h = bs.left_sum_hessian; L.int_g = bs.left_int_g; L.int_h = bs.left_int_h;
+    L.count = bs.left_count;
+    R.sum_g = bs.right_sum_gradient; R.sum_h = bs.right_sum_hessian; R.int_g = bs.right_int_g; R.int_h = bs.right_int_h;
+    R.count = bs.right_count;
+    L.splittable = parent_spl; R.splittable = parent_spl;
+    L.best.Reset(); R.best.Reset();
+  }
+
+  // ---------------------------------------------------------------- GBDT (A.9)
+  bool TrainOneIter() {
+    double init_score = 0.0;
+    if (models.empty() && !shards[0].ds->has_init_score && cfg.boost_from_average && obj != OBJ_LAMBDARANK) {
+      double v = BoostFromScore();
+      // ObtainAutomaticInitialScore: GlobalSyncUpByMean over machines (every machine holds the same value)
+      if (S > 1) { double acc = 0.0; for (int s = 0; s < S; ++s) acc += v; v = acc / S; }
+      if (std::fabs(v) > kEpsilon) {
+        init_score = v;
+        for (auto& sh : shards) for (auto& x : sh.score) x += v;
+      }
+    }
+    GetGradients();
+    bool should_continue = false;
+    std::unique_ptr<Tree> tree(new Tree(2));
+    if (need_train && F > 0) tree = TrainTree();
+    if (tree->num_leaves > 1) {
+      should_continue = true;
+      tree->Shrinkage(cfg.learning_rate);
+      for (auto& sh : shards) {
+        for (int l = 0; l < tree->num_leaves; ++l) {
+          const double out = tree->leaf_value[l];
+          const data_size_t b = sh.leaf_begin[l], n = sh.leaf_count[l];
+          for (data_size_t i = 0; i < n; ++i) sh.score[sh.indices[b + i]] += out;
+        }
+      }
+      if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
+    } else if (models.empty()) {
+      double output = need_train ? init_score : BoostFromScore();
+      tree->AsConstantTree(output);
+      for (auto& sh : shards) for (auto& x : sh.score) x += output;
+    }
+    models.push_back(std::move(tree));
+    if (!should_continue) {
+      if (models.size() > 1) models.pop_back();
+      return true;
+    }
+    ++iter;
+    return false;
+  }
+
+  std::string ObjectiveString() const {
+    if (obj == OBJ_BINARY) return "binary sigmoid:" + FmtG(cfg.sigmoid);
+    if (obj == OBJ_L2) return "regression";
+    return "lambdarank";
+  }
+
+  std::string SaveModelToString() const {
+    const Dataset* d = shards[0].ds;
+    std::string s;
+    s += "tree\n";
+    s += "version=v3\n";
+    s += "num_class=1\n";
+    s += "num_tree_per_iteration=1\n";
+    s += "label_index=0\n";
+    s += "max_feature_idx=" + std::to_string(d->num_total_features - 1) + "\n";
+    s += "objective=" + ObjectiveString() + "\n";
+    s += "feature_names=";
+    for (int j = 0; j < d->num_total_features; ++j) { if (j) s += ' '; s += d->feature_names[j]; }
+    s += "\nfeature_infos=";
+    for (int j = 0; j < d->num_total_features; ++j) {
+      if (j) s += ' ';
+      const BinMapper& m = d->mappers[j];
+      if (m.is_trivial) s += "none"; else s += "[" + FmtG17(m.min_val) + ":" + FmtG17(m.max_val) + "]";
+    }
+    s += "\n";
+    std::vector<std::string> blocks;
+    for (size_t i = 0; i < models.size(); ++i) blocks.push_back("Tree=" + std::to_string(i) + "\n" + models[i]->ToString() + "\n");
+    s += "tree_sizes=";
+    for (size_t i = 0; i < blocks.size(); ++i) { if (i) s += ' '; s += std::to_string(blocks[i].size()); }
+    s += "\n\n";
+    for (auto& b : blocks) s += b;
+    s += "end of trees\n\n";
+    // feature importances (split counts, descending, stable by feature index)
+    std::vector<int> imp(d->num_total_features, 0);
+    for (auto& t : models) for (int i = 0; i < t->num_leaves - 1; ++i) imp[t->split_feature[i]]++;
+    std::vector<int> order;
+    for (int j = 0; j < d->num_total_features; ++j) if (imp[j] > 0) order.push_back(j);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return imp[a] > imp[b]; });
+    s += "feature_importances:\n";
+    for (int j : order) s += d->feature_names[j] + "=" + std::to_string(imp[j]) + "\n";
+    s += "\nparameters:\n";
+    for (auto& kv : cfg.raw) s += "[" + kv.first + ": " + kv.second + "]\n";
+    s += "end of parameters\n\npandas_categorical:null\n";
+    return s;
+  }
+
+  void PredictRaw(const double* data, int nrow, int ncol, double* out) const {
+    for (int i = 0; i < nrow; ++i) {
+      double v = 0.0;
+      for (auto& t : models) v += t->Predict(data + static_cast<size_t>(i) * ncol);
+      out[i] = v;
+    }
+  }
+};
+
+}  // namespace orc
