@@ -1,0 +1,141 @@
+/*
+ * C ABI of the B200-native LightGBM training library (lib_lightgbm.so built from synapseml_b200/csrc).
+ *
+ * Every entry point below has the name, argument order and meaning of the LightGBM C API function that the reference
+ * binds through SWIG/JNI (com.microsoft.ml.lightgbm.lightgbmlib); the reference call site each one serves is cited
+ * (paths relative to /root/reference/lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/).
+ * Conventions (reference: LightGBMUtils.scala:15-27): return 0 on success and -1 on error; the message is then available
+ * from LGBM_GetLastError() on the calling thread.  Handles are opaque.  The caller owns every input buffer and may free
+ * it as soon as the call returns (the library copies what it keeps).  No exception crosses this boundary.
+ *
+ * All compute runs on one B200 per process (device = parameter gpu_device_id, else $LOCAL_RANK, else 0); there is no CPU
+ * path: a call that needs the GPU fails with an error when none is usable.
+ */
+#ifndef LIGHTGBM_B200_C_API_H_
+#define LIGHTGBM_B200_C_API_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* DatasetHandle;
+typedef void* BoosterHandle;
+typedef void* ByteBufferHandle;
+
+#define C_API_DTYPE_FLOAT32 (0)
+#define C_API_DTYPE_FLOAT64 (1)
+#define C_API_DTYPE_INT32 (2)
+#define C_API_DTYPE_INT64 (3)
+
+#define C_API_PREDICT_NORMAL (0)
+#define C_API_PREDICT_RAW_SCORE (1)
+#define C_API_PREDICT_LEAF_INDEX (2)
+#define C_API_PREDICT_CONTRIB (3)
+
+/* LightGBMUtils.scala:18,25 — thread-local message of the last failed call */
+const char* LGBM_GetLastError(void);
+
+/* ---------------------------------------------------------------- Dataset */
+
+/* dataset/ReferenceDatasetUtils.scala:38-47 — bin-boundary search (kernel K1) on the driver-side sample laid out by
+ * dataset/SampledData.scala:26-96 (column-major, non-zero values only). */
+int LGBM_DatasetCreateFromSampledColumn(double** sample_data, int** sample_indices, int32_t ncol, const int* num_per_col,
+                                        int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
+                                        const char* parameters, DatasetHandle* out);
+
+/* dataset/ReferenceDatasetUtils.scala:52-55 — bin mappers as an opaque byte buffer (shipped driver -> executors) */
+int LGBM_DatasetSerializeReferenceToBinary(DatasetHandle handle, ByteBufferHandle* out, int32_t* out_len);
+/* dataset/ReferenceDatasetUtils.scala:107 / :115 */
+int LGBM_ByteBufferGetAt(ByteBufferHandle handle, int32_t index, uint8_t* out_val);
+int LGBM_ByteBufferFree(ByteBufferHandle handle);
+/* bulk alternative to the per-byte LGBM_ByteBufferGetAt loop: copies the whole buffer */
+int LGBM_ByteBufferCopy(ByteBufferHandle handle, uint8_t* out, int32_t out_capacity);
+
+/* dataset/ReferenceDatasetUtils.scala:121-138 — empty num_row-row dataset with the serialized bin mappers */
+int LGBM_DatasetCreateFromSerializedReference(const void* ref_buffer, int32_t ref_buffer_size, int64_t num_row,
+                                              int32_t num_classes, const char* parameters, DatasetHandle* out);
+
+/* StreamingPartitionTask.scala:349-364 (validation data) — empty dataset sharing another dataset's bin mappers */
+int LGBM_DatasetCreateByReference(const DatasetHandle reference, int64_t num_total_row, DatasetHandle* out);
+
+/* dataset/ReferenceDatasetUtils.scala:87-94 */
+int LGBM_DatasetInitStreaming(DatasetHandle dataset, int32_t has_weights, int32_t has_init_scores, int32_t has_queries,
+                              int32_t nclasses, int32_t nthreads, int32_t omp_max_threads);
+
+/* StreamingPartitionTask.scala:220-231 — row binning (kernel K2).  Thread-safe for distinct tid and disjoint row ranges. */
+int LGBM_DatasetPushRowsWithMetadata(DatasetHandle dataset, const void* data, int data_type, int32_t nrow, int32_t ncol,
+                                     int32_t start_row, const float* label, const float* weight, const double* init_score,
+                                     const int32_t* query, int32_t tid);
+
+/* StreamingPartitionTask.scala:358 / :143,168 */
+int LGBM_DatasetSetWaitForManualFinish(DatasetHandle dataset, int wait);
+int LGBM_DatasetMarkFinished(DatasetHandle dataset);
+
+/* dataset/DatasetAggregator.scala:413-421 (bulk mode): bin a whole row-major matrix; reference may be NULL */
+int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                              const char* parameters, const DatasetHandle reference, DatasetHandle* out);
+
+/* dataset/LightGBMDataset.scala:115,149,163 / :29 — field_name in {label, weight, init_score, group} */
+int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element, int type);
+int LGBM_DatasetGetField(DatasetHandle handle, const char* field_name, int* out_len, const void** out_ptr, int* out_type);
+
+/* dataset/LightGBMDataset.scala:54 / :65 / :182 / :191 */
+int LGBM_DatasetGetNumData(DatasetHandle handle, int* out);
+int LGBM_DatasetGetNumFeature(DatasetHandle handle, int* out);
+int LGBM_DatasetSetFeatureNames(DatasetHandle handle, const char** feature_names, int num_feature_names);
+int LGBM_DatasetFree(DatasetHandle handle);
+
+/* ---------------------------------------------------------------- Booster */
+
+/* booster/LightGBMBooster.scala:241 (from TrainUtils.scala:16-29) */
+int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out);
+/* booster/LightGBMBooster.scala:355-365 (from TrainUtils.scala:98-135) — one boosting iteration (kernels K3-K8) */
+int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished);
+/* booster/LightGBMBooster.scala:372-392 */
+int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished);
+/* booster/LightGBMBooster.scala:316-323 (learning-rate schedule through the delegate) */
+int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters);
+/* booster/LightGBMBooster.scala:272-278 (SWIG wrapper LGBM_BoosterSaveModelToStringSWIG grows the buffer and retries) */
+int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration, int feature_importance_type,
+                                  int64_t buffer_len, int64_t* out_len, char* out_str);
+/* booster/LightGBMBooster.scala:163,193,173,183 */
+int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len);
+int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len);
+int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_iteration);
+int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
+int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration);
+/* booster/LightGBMBooster.scala:331-350 — raw training scores (data_idx 0) */
+int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result);
+/* booster/LightGBMBooster.scala:155 */
+int LGBM_BoosterFree(BoosterHandle handle);
+
+/* ---------------------------------------------------------------- Network */
+
+/* NetworkManager.scala:195-218 — machines = "host:port,host:port,...".  num_machines == 1 is a no-op.  Otherwise the
+ * list is used once to hand rank 0's NCCL unique id to the other ranks; collectives then run over NVLink. */
+int LGBM_NetworkInit(const char* machines, int local_listen_port, int listen_time_out, int num_machines);
+/* BasePartitionTask.scala:282 */
+int LGBM_NetworkFree(void);
+
+/* ---------------------------------------------------------------- Extensions (no lightgbmlib counterpart)
+ * Introspection used by the parity tests and by bench.py; not called by the Scala layer. */
+int LGBM_B200_DatasetGetFeatureInfo(DatasetHandle handle, int feature, int* num_bin, int* missing_type, int* default_bin,
+                                    int* most_freq_bin, int* is_trivial, double* min_val, double* max_val);
+int LGBM_B200_DatasetGetBinUpperBounds(DatasetHandle handle, int feature, double* out);
+int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out);
+int LGBM_B200_DatasetCopyBinColumn(DatasetHandle handle, int inner_feature, uint8_t* out);
+int LGBM_B200_DatasetCopyRowMajor(DatasetHandle handle, int64_t row, int64_t nrows, int* out_stride, uint8_t* out);
+int LGBM_B200_BoosterGetGradients(BoosterHandle handle, float* grad, float* hess);
+int LGBM_B200_BoosterGetQuantGradients(BoosterHandle handle, int8_t* grad, int8_t* hess, double* scales);
+int LGBM_B200_BoosterRootHistogram(BoosterHandle handle, int64_t* out /* F_used*256*2 */);
+int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float* out_ms);
+int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable);
+int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches);
+int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIGHTGBM_B200_C_API_H_ */

@@ -1,0 +1,524 @@
+#include "booster.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "kernels.cuh"
+
+namespace lgb {
+
+std::string FormatG17(double v);
+std::string FormatG(double v);
+
+namespace {
+constexpr int kNumSms = 148;
+
+template <typename K>
+void SetSmem(K kernel, size_t bytes) {
+  LGB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+}
+constexpr size_t kHistSmem = size_t(4) * kBins * 32 * sizeof(unsigned int);   // 128 KB in both modes
+}  // namespace
+
+Booster::Booster(Dataset* train, const char* params) : ds_(train) {
+  LGB_CHECK(train != nullptr, "BoosterCreate: training dataset is null");
+  LGB_CHECK(train->finished, "BoosterCreate: the training dataset is not finished (LGBM_DatasetMarkFinished was not called)");
+  LGB_CHECK(train->num_data > 0, "BoosterCreate: the training dataset has no rows");
+  cfg_ = train->cfg;
+  cfg_.raw.clear();
+  cfg_.Set(params ? params : "");
+  // dataset-time parameters the booster string does not repeat keep their dataset values
+  for (auto& kv : train->cfg.raw)
+    if (!cfg_.raw.count(kv.first)) cfg_.raw[kv.first] = kv.second;
+  g_verbosity = cfg_.verbosity;
+  LGB_CHECK(cfg_.boosting == "gbdt", "boosting_type=%s is not supported by this library yet (gbdt only)", cfg_.boosting.c_str());
+  LGB_CHECK(cfg_.tree_learner == "serial" || cfg_.tree_learner == "data" || cfg_.tree_learner == "data_parallel",
+            "tree_learner=%s is not supported by this library (data_parallel / serial)", cfg_.tree_learner.c_str());
+  LGB_CHECK(cfg_.num_leaves >= 2 && cfg_.num_leaves <= 1024, "num_leaves=%d is outside [2, 1024]", cfg_.num_leaves);
+  LGB_CHECK(!cfg_.zero_as_missing, "zero_as_missing=true is not supported by this library yet");
+  LGB_CHECK(cfg_.num_grad_quant_bins >= 2 && cfg_.num_grad_quant_bins <= 64, "num_grad_quant_bins=%d is outside [2, 64]", cfg_.num_grad_quant_bins);
+  device_ = train->device;
+  LGB_CUDA(cudaSetDevice(device_));
+  LGB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  net_ = Network::Get();
+  net_->EnsureComm(device_);
+  n_ = train->num_data;
+  F_ = train->num_features();
+  has_weights_ = train->has_weight;
+  // global row count and this shard's offset (rank order = row order, BasePartitionTask.scala:92-112)
+  std::vector<long long> all;
+  net_->HostAllGatherInt64(n_, &all);
+  n_global_ = 0;
+  row_offset_ = 0;
+  for (int r = 0; r < net_->world(); ++r) {
+    if (r < net_->rank()) row_offset_ += all[r];
+    n_global_ += all[r];
+  }
+  LGB_CHECK(n_global_ < (int64_t(1) << 31), "more than 2^31 rows in total are not supported");
+  InitObjective();
+  lp_.l1 = cfg_.lambda_l1; lp_.l2 = cfg_.lambda_l2; lp_.max_delta_step = cfg_.max_delta_step;
+  lp_.min_gain_to_split = cfg_.min_gain_to_split; lp_.min_sum_hessian = cfg_.min_sum_hessian_in_leaf;
+  lp_.learning_rate = cfg_.learning_rate; lp_.min_data_in_leaf = cfg_.min_data_in_leaf; lp_.max_depth = cfg_.max_depth;
+  lp_.num_leaves = cfg_.num_leaves; lp_.num_features = F_;
+  lp_.quantized = cfg_.use_quantized_grad; lp_.dp = net_->active();
+  lp_.num_grad_quant_bins = cfg_.num_grad_quant_bins; lp_.stochastic_rounding = cfg_.stochastic_rounding;
+  lp_.const_hessian = (obj_ == kL2 && !has_weights_);
+  lp_.seed = static_cast<unsigned int>(cfg_.seed);
+
+  const int L = cfg_.num_leaves;
+  d_score_.AllocZero(n_);
+  if (train->has_init_score) LGB_CUDA(cudaMemcpy(d_score_.p, train->d_init_score.p, sizeof(double) * n_, cudaMemcpyDeviceToDevice));
+  d_grad_.Alloc(n_); d_hess_.Alloc(n_);
+  if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
+  d_idx_[0].Alloc(n_); d_idx_[1].Alloc(n_);
+  d_flags_.Alloc(n_ / 32 + 2 * kPartThreads);
+  d_part_counts_.AllocZero(kPartBlocks);
+  const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
+  d_hist_pool_.Alloc(hist_elems * L);
+  d_hist_work_.Alloc(hist_elems);
+  d_leaves_.AllocZero(L);
+  d_ctrl_.AllocZero(1);
+  d_feat_best_.Alloc(static_cast<size_t>(2) * std::max(F_, 1));
+  d_splittable_.Alloc(static_cast<size_t>(L) * std::max(F_, 1));
+  d_sorted_leaf_.AllocZero(2 * L);
+  // tree arrays blob: 8 int arrays [L], decision_type [L], split_gain [L], 4 double arrays [L]
+  {
+    const size_t ints = 8 * sizeof(int) * L, chars = RoundUp<size_t>(L, 8), floats = RoundUp<size_t>(sizeof(float) * L, 8), dbl = 4 * sizeof(double) * L;
+    tree_blob_bytes_ = dbl + ints + floats + chars;
+    d_tree_blob_.AllocZero(tree_blob_bytes_);
+    h_tree_blob_.resize(tree_blob_bytes_);
+    unsigned char* b = d_tree_blob_.p;
+    tree_dev_.leaf_value = reinterpret_cast<double*>(b); tree_dev_.leaf_weight = tree_dev_.leaf_value + L;
+    tree_dev_.internal_value = tree_dev_.leaf_weight + L; tree_dev_.internal_weight = tree_dev_.internal_value + L;
+    int* ip = reinterpret_cast<int*>(b + dbl);
+    tree_dev_.left_child = ip; tree_dev_.right_child = ip + L; tree_dev_.split_feature_inner = ip + 2 * L;
+    tree_dev_.threshold_in_bin = ip + 3 * L; tree_dev_.leaf_count = ip + 4 * L; tree_dev_.internal_count = ip + 5 * L;
+    tree_dev_.leaf_parent = ip + 6 * L; tree_dev_.leaf_depth = ip + 7 * L;
+    tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
+    tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+  }
+  SetSmem(k_hist<4, 4, false>, kHistSmem); SetSmem(k_hist<2, 4, false>, kHistSmem); SetSmem(k_hist<1, 4, false>, kHistSmem);
+  SetSmem(k_hist<4, 2, true>, kHistSmem); SetSmem(k_hist<2, 2, true>, kHistSmem); SetSmem(k_hist<1, 2, true>, kHistSmem);
+  LGB_CUDA(cudaStreamSynchronize(stream_));
+}
+
+Booster::~Booster() {
+  cudaSetDevice(device_);
+  if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
+  for (auto& e : hist_events_) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+}
+
+void Booster::Sync() const { LGB_CUDA(cudaStreamSynchronize(stream_)); }
+
+void Booster::ResetParameter(const char* params) {
+  Config c;
+  c.Set(params ? params : "");
+  if (c.raw.count("learning_rate")) { cfg_.learning_rate = c.learning_rate; lp_.learning_rate = c.learning_rate; cfg_.raw["learning_rate"] = c.raw["learning_rate"]; }
+}
+
+// ---------------------------------------------------------------------------------------------------- objectives
+void Booster::InitObjective() {
+  const std::vector<float>& label = ds_->label;
+  if (cfg_.objective == "binary") {
+    obj_ = kBinary;
+    double cnt[2] = {0.0, 0.0};
+    for (float l : label) cnt[l > 0 ? 1 : 0] += 1.0;
+    net_->HostAllReduceSum(cnt, 2);    // label counts are summed over machines (a shard with one class still trains)
+    const double neg = cnt[0], pos = cnt[1];
+    need_train_ = !(pos == 0 || neg == 0);
+    if (!need_train_) LogWarning("Contains only one class");
+    label_weights_[0] = label_weights_[1] = 1.0;
+    if (cfg_.is_unbalance && pos > 0 && neg > 0) {
+      if (pos > neg) { label_weights_[1] = 1.0; label_weights_[0] = pos / neg; }
+      else { label_weights_[1] = neg / pos; label_weights_[0] = 1.0; }
+    }
+    label_weights_[1] *= cfg_.scale_pos_weight;
+  } else if (cfg_.objective == "regression") {
+    obj_ = kL2;
+  } else if (cfg_.objective == "lambdarank") {
+    obj_ = kLambdarank;
+    LGB_CHECK(!ds_->query_boundaries.empty(), "lambdarank needs query information (a group column)");
+    std::vector<double> label_gain = cfg_.label_gain;
+    if (label_gain.empty()) for (int i = 0; i < 31; ++i) label_gain.push_back(static_cast<double>((1LL << i) - 1));
+    const int kMaxPosition = 10000;
+    std::vector<double> discount(kMaxPosition);
+    for (int i = 0; i < kMaxPosition; ++i) discount[i] = 1.0 / std::log2(2.0 + i);
+    const auto& qb = ds_->query_boundaries;
+    const int nq = static_cast<int>(qb.size()) - 1;
+    std::vector<double> inv(nq);
+    max_query_len_ = 0;
+    for (float l : label) LGB_CHECK(l >= 0 && static_cast<int>(l) < static_cast<int>(label_gain.size()) && l == static_cast<int>(l),
+                                    "lambdarank labels must be integers in [0, %d)", static_cast<int>(label_gain.size()));
+    for (int q = 0; q < nq; ++q) {
+      const int b = qb[q], cnt = qb[q + 1] - b;
+      LGB_CHECK(cnt <= kMaxPosition, "A query has %d rows; the limit is %d", cnt, kMaxPosition);
+      max_query_len_ = std::max(max_query_len_, cnt);
+      // CalMaxDCGAtK
+      std::vector<int> label_cnt(label_gain.size(), 0);
+      for (int i = 0; i < cnt; ++i) ++label_cnt[static_cast<int>(label[b + i])];
+      int top_label = static_cast<int>(label_gain.size()) - 1;
+      int k = std::min(cfg_.lambdarank_truncation_level, cnt);
+      double ret = 0.0;
+      for (int j = 0; j < k; ++j) {
+        while (top_label > 0 && label_cnt[top_label] <= 0) top_label -= 1;
+        if (top_label < 0) break;
+        ret += discount[j] * label_gain[top_label];
+        label_cnt[top_label] -= 1;
+      }
+      if (ret > 0.0) ret = 1.0f / ret;
+      inv[q] = ret;
+    }
+    const size_t bins = 1024 * 1024;
+    min_sigmoid_input_ = -50.0 / cfg_.sigmoid / 2;
+    max_sigmoid_input_ = -min_sigmoid_input_;
+    sigmoid_table_idx_factor_ = bins / (max_sigmoid_input_ - min_sigmoid_input_);
+    std::vector<double> table(bins);
+    for (size_t i = 0; i < bins; ++i) {
+      const double sc = i / sigmoid_table_idx_factor_ + min_sigmoid_input_;
+      table[i] = 1.0f / (1.0f + std::exp(sc * cfg_.sigmoid));
+    }
+    d_sigmoid_table_.Alloc(bins); LGB_CUDA(cudaMemcpy(d_sigmoid_table_.p, table.data(), sizeof(double) * bins, cudaMemcpyHostToDevice));
+    d_inv_max_dcg_.Alloc(nq); LGB_CUDA(cudaMemcpy(d_inv_max_dcg_.p, inv.data(), sizeof(double) * nq, cudaMemcpyHostToDevice));
+    d_label_gain_.Alloc(label_gain.size()); LGB_CUDA(cudaMemcpy(d_label_gain_.p, label_gain.data(), sizeof(double) * label_gain.size(), cudaMemcpyHostToDevice));
+    d_discount_.Alloc(kMaxPosition); LGB_CUDA(cudaMemcpy(d_discount_.p, discount.data(), sizeof(double) * kMaxPosition, cudaMemcpyHostToDevice));
+  } else {
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, regression, lambdarank)");
+  }
+}
+
+double Booster::BoostFromScoreLocalSums(double* suml, double* sumw) const {
+  const std::vector<float>& label = ds_->label;
+  const std::vector<float>& w = ds_->weight;
+  double sl = 0.0, sw = 0.0;
+  if (obj_ == kBinary) {
+    if (has_weights_) { for (int64_t i = 0; i < n_; ++i) { sl += (label[i] > 0) * w[i]; sw += w[i]; } }
+    else { sw = static_cast<double>(n_); for (int64_t i = 0; i < n_; ++i) sl += (label[i] > 0); }
+  } else {
+    if (has_weights_) { for (int64_t i = 0; i < n_; ++i) { sl += label[i] * w[i]; sw += w[i]; } }
+    else { sw = static_cast<double>(n_); for (int64_t i = 0; i < n_; ++i) sl += label[i]; }
+  }
+  *suml = sl; *sumw = sw;
+  return 0.0;
+}
+
+void Booster::ComputeGradients() {
+  const int n = static_cast<int>(n_);
+  const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
+  const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
+  if (obj_ == kBinary) {
+    k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_.p, d_hess_.p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
+  } else if (obj_ == kL2) {
+    k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_.p, d_hess_.p, n);
+  } else {
+    LambdarankArgs a;
+    a.score = d_score_.p; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
+    a.inv_max_dcg = d_inv_max_dcg_.p; a.label_gain = d_label_gain_.p; a.discount = d_discount_.p; a.sigmoid_table = d_sigmoid_table_.p;
+    a.grad = d_grad_.p; a.hess = d_hess_.p; a.sigmoid = cfg_.sigmoid; a.min_sigmoid_input = min_sigmoid_input_;
+    a.max_sigmoid_input = max_sigmoid_input_; a.idx_factor = sigmoid_table_idx_factor_;
+    a.truncation_level = cfg_.lambdarank_truncation_level; a.norm = cfg_.lambdarank_norm; a.table_size = 1024 * 1024;
+    a.max_cnt = max_query_len_;
+    const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
+    const size_t smem = static_cast<size_t>(max_query_len_) * (sizeof(double) + sizeof(float) + sizeof(int));
+    static size_t smem_set = 0;
+    if (smem > smem_set) { SetSmem(k_grad_lambdarank, smem); smem_set = smem; }
+    k_grad_lambdarank<<<nq, 256, smem, stream_>>>(a);
+  }
+  LGB_CUDA(cudaGetLastError());
+  ++launches_;
+}
+
+void Booster::PrepareGradients() {
+  const int n = static_cast<int>(n_);
+  const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
+  k_absmax<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_.p);
+  if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_.p->max_abs_g_bits, 2, stream_);
+  k_scales<<<1, 1, 0, stream_>>>(d_ctrl_.p, lp_);
+  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_.p, lp_, static_cast<unsigned int>(iter_),
+                                        static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p);
+  LGB_CUDA(cudaGetLastError());
+  launches_ += 3;
+}
+
+// ---------------------------------------------------------------------------------------------------- tree learner
+void Booster::LaunchHist(bool root) {
+  const BinLayout& lay = ds_->layout;
+  const int R = lay.rows_per_step;
+  const bool flt = !lp_.quantized;
+  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
+  const int tiles = CeilDiv(F_, ft);
+  const int row_ctas = std::max(1, kNumSms / tiles);
+  dim3 grid(row_ctas, tiles);
+  int rows_per_flush;
+  if (flt) {
+    rows_per_flush = kFixRowsPerCopy * R;
+  } else {
+    const int qb = cfg_.num_grad_quant_bins;
+    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
+    rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
+  }
+  LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, d_hist_work_.bytes(), stream_));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (time_hist_) {
+    if (hist_events_used_ == hist_events_.size()) {
+      cudaEvent_t a, b;
+      LGB_CUDA(cudaEventCreate(&a)); LGB_CUDA(cudaEventCreate(&b));
+      hist_events_.emplace_back(a, b);
+    }
+    e0 = hist_events_[hist_events_used_].first; e1 = hist_events_[hist_events_used_].second;
+    ++hist_events_used_;
+    LGB_CUDA(cudaEventRecord(e0, stream_));
+  }
+#define LAUNCH_HIST(RR, BPL, FLT)                                                                                      \
+  k_hist<RR, BPL, FLT><<<grid, kHistThreads, kHistSmem, stream_>>>(ds_->d_rm.p, lay.rm_stride, d_gh16_.p, d_ghfix_.p,   \
+                                                                   d_idx_[0].p, d_idx_[1].p, d_leaves_.p, d_ctrl_.p,    \
+                                                                   d_hist_work_.p, F_, root ? 1 : 0, rows_per_flush)
+  if (!flt) {
+    if (R == 4) LAUNCH_HIST(4, 4, false); else if (R == 2) LAUNCH_HIST(2, 4, false); else LAUNCH_HIST(1, 4, false);
+  } else {
+    if (R == 4) LAUNCH_HIST(4, 2, true); else if (R == 2) LAUNCH_HIST(2, 2, true); else LAUNCH_HIST(1, 2, true);
+  }
+#undef LAUNCH_HIST
+  LGB_CUDA(cudaGetLastError());
+  if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
+  ++launches_;
+  if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, d_hist_work_.n, stream_);
+}
+
+void Booster::TrainTree(HostTree* out) {
+  const int L = cfg_.num_leaves;
+  const int n = static_cast<int>(n_);
+  hist_events_used_ = 0;
+  k_tree_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, L, n, static_cast<int>(n_global_));
+  LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
+  ++launches_;
+  const int find_grid = CeilDiv(F_, 8);
+  LaunchHist(true);
+  if (lp_.quantized) k_find<true><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 1);
+  else k_find<false><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 1);
+  ++launches_;
+  for (int split = 0; split < L - 1; ++split) {
+    k_select<<<1, 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, d_feat_best_.p, tree_dev_, ds_->d_fmeta.p, lp_);
+    k_part_count<<<kPartBlocks, kPartThreads, 0, stream_>>>(ds_->d_cm.p, ds_->n_pad, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
+    k_part_scatter<<<kPartBlocks, kPartThreads, 0, stream_>>>(d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_leaves_.p,
+                                                              d_flags_.p, d_part_counts_.p, tree_dev_, d_splittable_.p, lp_);
+    launches_ += 3;
+    if (split < L - 2) {
+      LaunchHist(false);
+      if (lp_.quantized) k_find<true><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 0);
+      else k_find<false><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 0);
+      ++launches_;
+    }
+  }
+  LGB_CUDA(cudaGetLastError());
+  FetchTree(out);
+}
+
+void Booster::FetchTree(HostTree* t) {
+  const int L = cfg_.num_leaves;
+  TreeCtrl hc;
+  LGB_CUDA(cudaMemcpyAsync(h_tree_blob_.data(), d_tree_blob_.p, tree_blob_bytes_, cudaMemcpyDeviceToHost, stream_));
+  LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_.p, sizeof(TreeCtrl), cudaMemcpyDeviceToHost, stream_));
+  Sync();
+  last_rows_visited_ += hc.hist_rows;
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, sizeof(long long), stream_));
+  const int nl = hc.num_leaves;
+  t->num_leaves = nl;
+  t->shrinkage = 1.0;
+  const unsigned char* b = h_tree_blob_.data();
+  const double* dv = reinterpret_cast<const double*>(b);
+  const size_t dbl = 4 * sizeof(double) * L, ints = 8 * sizeof(int) * L, floats = RoundUp<size_t>(sizeof(float) * L, 8);
+  const int* ip = reinterpret_cast<const int*>(b + dbl);
+  const float* fp = reinterpret_cast<const float*>(b + dbl + ints);
+  const signed char* cp = reinterpret_cast<const signed char*>(b + dbl + ints + floats);
+  const int ni = std::max(nl - 1, 0);
+  t->leaf_value.assign(dv, dv + nl); t->leaf_weight.assign(dv + L, dv + L + nl);
+  t->internal_value.assign(dv + 2 * L, dv + 2 * L + ni); t->internal_weight.assign(dv + 3 * L, dv + 3 * L + ni);
+  t->left_child.assign(ip, ip + ni); t->right_child.assign(ip + L, ip + L + ni);
+  t->split_feature_inner.assign(ip + 2 * L, ip + 2 * L + ni); t->threshold_in_bin.assign(ip + 3 * L, ip + 3 * L + ni);
+  t->leaf_count.assign(ip + 4 * L, ip + 4 * L + nl); t->internal_count.assign(ip + 5 * L, ip + 5 * L + ni);
+  t->leaf_depth.assign(ip + 7 * L, ip + 7 * L + nl);
+  t->split_gain.assign(fp, fp + ni);
+  t->decision_type.assign(cp, cp + ni);
+  t->split_feature.resize(ni); t->threshold.resize(ni);
+  for (int i = 0; i < ni; ++i) {
+    const int inner = t->split_feature_inner[i];
+    t->split_feature[i] = ds_->used[inner];
+    t->threshold[i] = ds_->mappers[ds_->used[inner]].upper[t->threshold_in_bin[i]];   // RealThreshold
+  }
+}
+
+void Booster::UpdateScores() {
+  const int L = cfg_.num_leaves;
+  const int n = static_cast<int>(n_);
+  k_sort_leaves<<<1, 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, d_sorted_leaf_.p, L);
+  k_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, d_leaves_.p, d_ctrl_.p,
+                                                                             d_sorted_leaf_.p, L, tree_dev_.leaf_value, cfg_.learning_rate, n);
+  LGB_CUDA(cudaGetLastError());
+  launches_ += 2;
+}
+
+// ---------------------------------------------------------------------------------------------------- GBDT
+bool Booster::UpdateOneIter() {
+  LGB_CUDA(cudaSetDevice(device_));
+  const double kEps = 1e-15f;
+  double init_score = 0.0;
+  if (models_.empty() && !ds_->has_init_score && cfg_.boost_from_average && obj_ != kLambdarank) {
+    double sums[2];
+    BoostFromScoreLocalSums(&sums[0], &sums[1]);
+    net_->HostAllReduceSum(sums, 2);
+    double v;
+    if (obj_ == kBinary) {
+      double pavg = sums[0] / sums[1];
+      pavg = std::min(pavg, 1.0 - kEps);
+      pavg = std::max<double>(pavg, kEps);
+      v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
+    } else {
+      v = sums[0] / sums[1];
+    }
+    if (net_->active()) {   // ObtainAutomaticInitialScore: mean over machines of identical values
+      double acc = 0.0;
+      for (int s = 0; s < net_->world(); ++s) acc += v;
+      v = acc / net_->world();
+    }
+    if (std::fabs(v) > kEps) {
+      init_score = v;
+      k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), v);
+      ++launches_;
+      LogInfo("Start training from score %lf", v);
+    }
+  }
+  HostTree tree;
+  tree.num_leaves = 1;
+  tree.leaf_value.assign(1, 0.0);
+  if (need_train_ && F_ > 0) {
+    ComputeGradients();
+    PrepareGradients();
+    TrainTree(&tree);
+  }
+  bool should_continue = false;
+  if (tree.num_leaves > 1) {
+    should_continue = true;
+    UpdateScores();
+    tree.Shrinkage(cfg_.learning_rate);
+    if (std::fabs(init_score) > kEps) tree.AddBias(init_score);
+  } else if (models_.empty()) {
+    double output = init_score;
+    if (!need_train_) {
+      double sums[2];
+      BoostFromScoreLocalSums(&sums[0], &sums[1]);
+      net_->HostAllReduceSum(sums, 2);
+      double pavg = std::max<double>(std::min(sums[0] / sums[1], 1.0 - kEps), kEps);
+      output = (obj_ == kBinary) ? std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid : sums[0] / sums[1];
+    }
+    tree.AsConstantTree(output);
+    k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), output);
+    ++launches_;
+  }
+  // per-iteration histogram timing (only when enabled by the bench / tests)
+  if (time_hist_ && hist_events_used_ > 0) {
+    Sync();
+    for (size_t i = 0; i < hist_events_used_; ++i) {
+      float ms = 0;
+      LGB_CUDA(cudaEventElapsedTime(&ms, hist_events_[i].first, hist_events_[i].second));
+      last_hist_ms_ += ms;
+    }
+  }
+  models_.push_back(std::move(tree));
+  if (!should_continue) {
+    LogWarning("Stopped training because there are no more leaves that meet the split requirements");
+    if (models_.size() > 1) models_.pop_back();
+    Sync();
+    return true;
+  }
+  ++iter_;
+  return false;
+}
+
+bool Booster::UpdateOneIterCustom(const float*, const float*) {
+  throw std::runtime_error("LGBM_BoosterUpdateOneIterCustom (custom objective) is not supported by this library yet");
+}
+
+ModelHeader Booster::MakeHeader() const {
+  ModelHeader h;
+  h.max_feature_idx = ds_->num_total_features - 1;
+  if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
+  else if (obj_ == kL2) h.objective = "regression";
+  else h.objective = "lambdarank";
+  h.feature_names = ds_->feature_names;
+  for (int j = 0; j < ds_->num_total_features; ++j) {
+    const BinMapperH& m = ds_->mappers[j];
+    h.feature_infos.push_back(m.is_trivial ? std::string("none") : "[" + FormatG17(m.min_val) + ":" + FormatG17(m.max_val) + "]");
+  }
+  for (auto& kv : cfg_.raw) h.parameters.emplace_back(kv.first, kv.second);
+  return h;
+}
+
+std::string Booster::SaveModelToString(int start_iteration, int num_iteration) const {
+  return ModelToString(MakeHeader(), models_, start_iteration, num_iteration);
+}
+
+void Booster::CopyScores(double* out) const {
+  LGB_CUDA(cudaSetDevice(device_));
+  Sync();
+  LGB_CUDA(cudaMemcpy(out, d_score_.p, sizeof(double) * n_, cudaMemcpyDeviceToHost));
+}
+
+void Booster::CopyGradients(float* g, float* h) const {
+  LGB_CUDA(cudaSetDevice(device_));
+  Sync();
+  LGB_CUDA(cudaMemcpy(g, d_grad_.p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(h, d_hess_.p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
+}
+
+void Booster::CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const {
+  LGB_CHECK(lp_.quantized, "quantized gradients exist only with use_quantized_grad=true");
+  LGB_CUDA(cudaSetDevice(device_));
+  Sync();
+  std::vector<uint16_t> tmp(n_);
+  LGB_CUDA(cudaMemcpy(tmp.data(), d_gh16_.p, sizeof(uint16_t) * n_, cudaMemcpyDeviceToHost));
+  for (int64_t i = 0; i < n_; ++i) { g[i] = static_cast<int8_t>(tmp[i] >> 8); h[i] = static_cast<int8_t>(tmp[i] & 0xff); }
+  TreeCtrl hc;
+  LGB_CUDA(cudaMemcpy(&hc, d_ctrl_.p, sizeof(TreeCtrl), cudaMemcpyDeviceToHost));
+  scales[0] = hc.grad_scale; scales[1] = hc.hess_scale;
+}
+
+void Booster::PredictRaw(const double* data, int nrow, int ncol, double* out) const {
+  LGB_CHECK(ncol == ds_->num_total_features, "PredictRaw: expected %d columns, got %d", ds_->num_total_features, ncol);
+  for (int i = 0; i < nrow; ++i) {
+    double v = 0.0;
+    for (const auto& t : models_) v += t.Predict(data + static_cast<size_t>(i) * ncol);
+    out[i] = v;
+  }
+}
+
+void Booster::DebugRootHistogram(long long* out) {
+  LGB_CUDA(cudaSetDevice(device_));
+  k_tree_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, cfg_.num_leaves,
+                                                                    static_cast<int>(n_), static_cast<int>(n_global_));
+  LaunchHist(true);
+  Sync();
+  LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, d_hist_work_.bytes(), cudaMemcpyDeviceToHost));
+}
+
+float Booster::TimeRootHistogram(int repeats) {
+  LGB_CUDA(cudaSetDevice(device_));
+  k_tree_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, cfg_.num_leaves,
+                                                                    static_cast<int>(n_), static_cast<int>(n_global_));
+  const bool was = time_hist_;
+  time_hist_ = true;
+  float total = 0;
+  for (int r = 0; r < repeats; ++r) {
+    hist_events_used_ = 0;
+    LaunchHist(true);
+    Sync();
+    float ms = 0;
+    LGB_CUDA(cudaEventElapsedTime(&ms, hist_events_[0].first, hist_events_[0].second));
+    total += ms;
+  }
+  time_hist_ = was;
+  return total / repeats;
+}
+
+}  // namespace lgb

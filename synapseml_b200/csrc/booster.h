@@ -1,0 +1,150 @@
+// Booster: objective kernels (K3), histogram construction (K4), sibling subtraction + split search (K5/K6), stable row
+// partition (K7), score update (K8) and the leaf-wise / GBDT drivers.  Everything that happens inside lightgbmlib
+// behind LGBM_BoosterCreate (lightgbm/.../booster/LightGBMBooster.scala:241, via TrainUtils.scala:16-29) and
+// LGBM_BoosterUpdateOneIter (LightGBMBooster.scala:355-365, driven by TrainUtils.scala:98-135) lives here.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "dataset.h"
+#include "model.h"
+#include "network.h"
+
+namespace lgb {
+
+struct SplitDev {
+  double gain;
+  int feature;          // inner index
+  int real_feature;
+  int threshold;
+  int default_left;
+  int left_count, right_count;
+  double left_output, right_output;
+  double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
+  long long left_int_g, left_int_h, right_int_g, right_int_h;
+};
+
+struct LeafDev {
+  int begin, count;      // local range of row indices
+  int buf;               // index buffer holding the range; -1: identity (the root before its first split)
+  int global_count;      // count the split finder uses: true count (serial) or the global estimate (data-parallel)
+  long long int_g, int_h;
+  double sum_g, sum_h;
+  int depth, hist_slot;
+  SplitDev best;
+};
+
+struct TreeCtrl {
+  int num_leaves;
+  int done;
+  int cur_leaf, new_leaf, cur_node;
+  int cur_feature, cur_threshold, cur_default_left, cur_nan_bin;
+  int src_begin, src_count, src_buf;
+  int smaller, larger, find, pending;
+  int parent_slot;
+  unsigned int max_abs_g_bits, max_abs_h_bits;
+  double grad_scale, hess_scale;      // quantized: int -> float scales.  float mode: fixed-point -> float (powers of two)
+  double inv_grad_scale, inv_hess_scale;
+  long long hist_rows;              // rows visited by histogram launches since the host last cleared it
+};
+
+struct TreeArraysDev {
+  int *left_child, *right_child, *split_feature_inner, *threshold_in_bin, *leaf_count, *internal_count, *leaf_parent, *leaf_depth;
+  signed char* decision_type;
+  float* split_gain;
+  double *leaf_value, *leaf_weight, *internal_value, *internal_weight;
+};
+
+struct LearnerParams {
+  double l1, l2, max_delta_step, min_gain_to_split, min_sum_hessian, learning_rate;
+  int min_data_in_leaf, max_depth, num_leaves, num_features;
+  int quantized, dp, num_grad_quant_bins, stochastic_rounding, const_hessian;
+  unsigned int seed;
+};
+
+class Booster {
+ public:
+  Booster(Dataset* train, const char* params);
+  ~Booster();
+  bool UpdateOneIter();
+  bool UpdateOneIterCustom(const float* grad, const float* hess);
+  void ResetParameter(const char* params);
+  std::string SaveModelToString(int start_iteration, int num_iteration) const;
+  int NumTrees() const { return static_cast<int>(models_.size()); }
+  int CurrentIteration() const { return iter_; }
+  void CopyScores(double* out) const;
+  void CopyGradients(float* g, float* h) const;
+  void CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const;
+  void PredictRaw(const double* data, int nrow, int ncol, double* out) const;
+  const Dataset* train() const { return ds_; }
+
+  // Kernel-level hooks used by parity tests, bench.py's roofline measurement and the profiler (no host sync inside):
+  // build the histogram of the whole dataset (root) with the current quantized / fixed-point gradients into out
+  // (F_used * 256 * 2 int64).
+  void DebugRootHistogram(long long* out);
+  float TimeRootHistogram(int repeats);
+  int64_t last_hist_rows_visited() const { return last_rows_visited_; }
+  double last_hist_ms() const { return last_hist_ms_; }
+  int launches() const { return launches_; }
+  void EnableHistTiming(bool on) { time_hist_ = on; }
+
+ private:
+  Dataset* ds_;
+  Config cfg_;
+  LearnerParams lp_{};
+  int device_ = 0;
+  cudaStream_t stream_ = nullptr;
+  Network* net_ = nullptr;
+  int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
+  int F_ = 0;
+  int iter_ = 0;
+  enum Obj { kBinary, kL2, kLambdarank } obj_ = kL2;
+  bool need_train_ = true, has_weights_ = false;
+  double label_weights_[2] = {1.0, 1.0};
+  std::vector<HostTree> models_;
+
+  // device state
+  DevBuf<double> d_score_;
+  DevBuf<float> d_grad_, d_hess_;
+  DevBuf<uint16_t> d_gh16_;          // quantized: (int8 grad << 8) | uint8 hess per row
+  DevBuf<int2> d_ghfix_;             // float mode: fixed-point (grad, hess) per row
+  DevBuf<int> d_idx_[2];
+  DevBuf<unsigned int> d_flags_;
+  DevBuf<int> d_part_counts_;
+  DevBuf<long long> d_hist_pool_, d_hist_work_;
+  DevBuf<LeafDev> d_leaves_;
+  DevBuf<TreeCtrl> d_ctrl_;
+  DevBuf<SplitDev> d_feat_best_;     // [2][F]
+  DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
+  DevBuf<unsigned char> d_tree_blob_;
+  TreeArraysDev tree_dev_{};
+  size_t tree_blob_bytes_ = 0;
+  std::vector<unsigned char> h_tree_blob_;
+  DevBuf<int> d_sorted_leaf_;        // [num_leaves] begin-sorted leaf ids + [num_leaves] begins
+  // lambdarank
+  DevBuf<double> d_sigmoid_table_, d_inv_max_dcg_, d_label_gain_, d_discount_;
+  double min_sigmoid_input_ = -50, max_sigmoid_input_ = 50, sigmoid_table_idx_factor_ = 1;
+  int max_query_len_ = 0;
+
+  // measurement
+  bool time_hist_ = false;
+  int64_t last_rows_visited_ = 0;
+  double last_hist_ms_ = 0;
+  int launches_ = 0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
+  size_t hist_events_used_ = 0;
+
+  void InitObjective();
+  double BoostFromScoreLocalSums(double* suml, double* sumw) const;
+  void ComputeGradients();
+  void PrepareGradients();           // absmax -> scales -> quantize / fixed point
+  void TrainTree(HostTree* out);
+  void LaunchHist(bool root);
+  void FetchTree(HostTree* out);
+  void UpdateScores();
+  ModelHeader MakeHeader() const;
+  void Sync() const;
+};
+
+}  // namespace lgb

@@ -1,0 +1,325 @@
+// extern "C" boundary: the LGBM_* entry points declared in include/lightgbm_b200_c_api.h.
+// Nothing throws across it: every call catches, stores a thread-local message and returns -1
+// (the reference turns -1 into an exception at LightGBMUtils.scala:15-20).
+#include "../../include/lightgbm_b200_c_api.h"
+
+#include <cstring>
+#include <exception>
+#include <memory>
+#include <string>
+
+#include "booster.h"
+#include "dataset.h"
+#include "network.h"
+
+using namespace lgb;
+
+namespace {
+thread_local std::string g_last_error = "Everything is fine";
+struct ByteBuffer { std::string data; };
+
+int Fail(const char* what) {
+  g_last_error = what;
+  return -1;
+}
+}  // namespace
+
+#define API_BEGIN() try {
+#define API_END()                                         \
+  }                                                       \
+  catch (std::exception & ex) { return Fail(ex.what()); } \
+  catch (...) { return Fail("unknown exception"); }      \
+  return 0;
+
+extern "C" {
+
+const char* LGBM_GetLastError(void) { return g_last_error.c_str(); }
+
+int LGBM_DatasetCreateFromSampledColumn(double** sample_data, int** sample_indices, int32_t ncol, const int* num_per_col,
+                                        int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
+                                        const char* parameters, DatasetHandle* out) {
+  API_BEGIN();
+  *out = Dataset::CreateFromSampledColumn(sample_data, sample_indices, ncol, num_per_col, num_sample_row, num_local_row,
+                                          num_dist_row, parameters);
+  API_END();
+}
+
+int LGBM_DatasetSerializeReferenceToBinary(DatasetHandle handle, ByteBufferHandle* out, int32_t* out_len) {
+  API_BEGIN();
+  auto bb = new ByteBuffer();
+  bb->data = static_cast<Dataset*>(handle)->SerializeReference();
+  *out = bb;
+  *out_len = static_cast<int32_t>(bb->data.size());
+  API_END();
+}
+
+int LGBM_ByteBufferGetAt(ByteBufferHandle handle, int32_t index, uint8_t* out_val) {
+  API_BEGIN();
+  auto bb = static_cast<ByteBuffer*>(handle);
+  LGB_CHECK(index >= 0 && static_cast<size_t>(index) < bb->data.size(), "ByteBuffer index %d out of range", index);
+  *out_val = static_cast<uint8_t>(bb->data[index]);
+  API_END();
+}
+
+int LGBM_ByteBufferCopy(ByteBufferHandle handle, uint8_t* out, int32_t out_capacity) {
+  API_BEGIN();
+  auto bb = static_cast<ByteBuffer*>(handle);
+  LGB_CHECK(static_cast<size_t>(out_capacity) >= bb->data.size(), "ByteBufferCopy: capacity %d < %zu", out_capacity, bb->data.size());
+  memcpy(out, bb->data.data(), bb->data.size());
+  API_END();
+}
+
+int LGBM_ByteBufferFree(ByteBufferHandle handle) {
+  API_BEGIN();
+  delete static_cast<ByteBuffer*>(handle);
+  API_END();
+}
+
+int LGBM_DatasetCreateFromSerializedReference(const void* ref_buffer, int32_t ref_buffer_size, int64_t num_row,
+                                              int32_t num_classes, const char* parameters, DatasetHandle* out) {
+  API_BEGIN();
+  (void)num_classes;
+  *out = Dataset::CreateFromSerializedReference(ref_buffer, ref_buffer_size, num_row, parameters);
+  API_END();
+}
+
+int LGBM_DatasetCreateByReference(const DatasetHandle reference, int64_t num_total_row, DatasetHandle* out) {
+  API_BEGIN();
+  *out = static_cast<const Dataset*>(reference)->CreateByReference(num_total_row);
+  API_END();
+}
+
+int LGBM_DatasetInitStreaming(DatasetHandle dataset, int32_t has_weights, int32_t has_init_scores, int32_t has_queries,
+                              int32_t nclasses, int32_t nthreads, int32_t omp_max_threads) {
+  API_BEGIN();
+  (void)omp_max_threads;
+  static_cast<Dataset*>(dataset)->InitStreaming(has_weights != 0, has_init_scores != 0, has_queries != 0, nclasses, nthreads);
+  API_END();
+}
+
+int LGBM_DatasetPushRowsWithMetadata(DatasetHandle dataset, const void* data, int data_type, int32_t nrow, int32_t ncol,
+                                     int32_t start_row, const float* label, const float* weight, const double* init_score,
+                                     const int32_t* query, int32_t tid) {
+  API_BEGIN();
+  static_cast<Dataset*>(dataset)->PushRows(data, data_type, nrow, ncol, start_row, label, weight, init_score, query, tid);
+  API_END();
+}
+
+int LGBM_DatasetSetWaitForManualFinish(DatasetHandle dataset, int wait) {
+  API_BEGIN();
+  static_cast<Dataset*>(dataset)->wait_for_manual_finish = wait != 0;
+  API_END();
+}
+
+int LGBM_DatasetMarkFinished(DatasetHandle dataset) {
+  API_BEGIN();
+  static_cast<Dataset*>(dataset)->MarkFinished();
+  API_END();
+}
+
+int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                              const char* parameters, const DatasetHandle reference, DatasetHandle* out) {
+  API_BEGIN();
+  LGB_CHECK(is_row_major == 1, "LGBM_DatasetCreateFromMat: only row-major input is supported (the reference always passes 1)");
+  LGB_CHECK(data_type == C_API_DTYPE_FLOAT64, "LGBM_DatasetCreateFromMat: only float64 input is supported");
+  std::unique_ptr<Dataset> ds;
+  if (reference != nullptr) {
+    ds.reset(static_cast<const Dataset*>(reference)->CreateByReference(nrow));
+  } else {
+    // no reference: bins are found from the first bin_construct_sample_cnt rows (the reference's samplingMode="fixed",
+    // LightGBMBase.scala:744-746); laid out as SampledData does (non-zero values per column)
+    Config c;
+    c.Set(parameters ? parameters : "");
+    const int ns = std::min<int>(nrow, c.bin_construct_sample_cnt);
+    const double* d = static_cast<const double*>(data);
+    std::vector<std::vector<double>> cols(ncol);
+    std::vector<std::vector<int>> idxs(ncol);
+    for (int i = 0; i < ns; ++i)
+      for (int j = 0; j < ncol; ++j) {
+        const double v = d[static_cast<size_t>(i) * ncol + j];
+        if (v != 0.0) { cols[j].push_back(v); idxs[j].push_back(i); }
+      }
+    std::vector<double*> dp(ncol);
+    std::vector<int*> ip(ncol);
+    std::vector<int> cnt(ncol);
+    for (int j = 0; j < ncol; ++j) { dp[j] = cols[j].data(); ip[j] = idxs[j].data(); cnt[j] = static_cast<int>(cols[j].size()); }
+    ds.reset(Dataset::CreateFromSampledColumn(dp.data(), ip.data(), ncol, cnt.data(), ns, nrow, nrow, parameters));
+  }
+  ds->wait_for_manual_finish = true;     // labels arrive through LGBM_DatasetSetField afterwards
+  ds->InitStreaming(false, false, false, 1, 1);
+  ds->PushRows(data, data_type, nrow, ncol, 0, nullptr, nullptr, nullptr, nullptr, 0);
+  *out = ds.release();
+  API_END();
+}
+
+int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element, int type) {
+  API_BEGIN();
+  auto ds = static_cast<Dataset*>(handle);
+  const std::string name(field_name);
+  LGB_CHECK(!ds->finished || name == "none", "LGBM_DatasetSetField(%s): the dataset is already finished", field_name);
+  if (name == "label") {
+    LGB_CHECK(type == C_API_DTYPE_FLOAT32 && num_element == ds->num_data, "label must be float32[num_data]");
+    ds->label.assign(static_cast<const float*>(field_data), static_cast<const float*>(field_data) + num_element);
+  } else if (name == "weight") {
+    LGB_CHECK(type == C_API_DTYPE_FLOAT32 && num_element == ds->num_data, "weight must be float32[num_data]");
+    ds->weight.assign(static_cast<const float*>(field_data), static_cast<const float*>(field_data) + num_element);
+    ds->has_weight = true;
+  } else if (name == "init_score") {
+    LGB_CHECK(type == C_API_DTYPE_FLOAT64 && num_element == ds->num_data, "init_score must be float64[num_data] (single class)");
+    ds->init_score.assign(static_cast<const double*>(field_data), static_cast<const double*>(field_data) + num_element);
+    ds->has_init_score = true;
+  } else if (name == "group" || name == "query") {
+    // cardinalities, DatasetUtils.scala:15-37 / LightGBMDataset.scala:171-176
+    LGB_CHECK(type == C_API_DTYPE_INT32, "group must be int32 cardinalities");
+    const int32_t* card = static_cast<const int32_t*>(field_data);
+    ds->query_boundaries.assign(1, 0);
+    for (int i = 0; i < num_element; ++i) ds->query_boundaries.push_back(ds->query_boundaries.back() + card[i]);
+    LGB_CHECK(ds->query_boundaries.back() == ds->num_data, "group cardinalities sum to %d, the dataset has %lld rows",
+              ds->query_boundaries.back(), (long long)ds->num_data);
+    ds->has_query = true;
+  } else {
+    throw std::runtime_error("Unknown field name " + name);
+  }
+  API_END();
+}
+
+int LGBM_DatasetGetField(DatasetHandle handle, const char* field_name, int* out_len, const void** out_ptr, int* out_type) {
+  API_BEGIN();
+  auto ds = static_cast<Dataset*>(handle);
+  const std::string name(field_name);
+  if (name == "label") { *out_len = static_cast<int>(ds->label.size()); *out_ptr = ds->label.data(); *out_type = C_API_DTYPE_FLOAT32; }
+  else if (name == "weight") { *out_len = static_cast<int>(ds->weight.size()); *out_ptr = ds->weight.data(); *out_type = C_API_DTYPE_FLOAT32; }
+  else if (name == "init_score") { *out_len = static_cast<int>(ds->init_score.size()); *out_ptr = ds->init_score.data(); *out_type = C_API_DTYPE_FLOAT64; }
+  else if (name == "group" || name == "query") { *out_len = static_cast<int>(ds->query_boundaries.size()); *out_ptr = ds->query_boundaries.data(); *out_type = C_API_DTYPE_INT32; }
+  else throw std::runtime_error("Unknown field name " + name);
+  API_END();
+}
+
+int LGBM_DatasetGetNumData(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<int>(static_cast<Dataset*>(handle)->num_data); API_END(); }
+int LGBM_DatasetGetNumFeature(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<Dataset*>(handle)->num_total_features; API_END(); }
+int LGBM_DatasetSetFeatureNames(DatasetHandle handle, const char** feature_names, int num_feature_names) {
+  API_BEGIN();
+  static_cast<Dataset*>(handle)->SetFeatureNames(feature_names, num_feature_names);
+  API_END();
+}
+int LGBM_DatasetFree(DatasetHandle handle) { API_BEGIN(); delete static_cast<Dataset*>(handle); API_END(); }
+
+int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out) {
+  API_BEGIN();
+  auto ds = static_cast<Dataset*>(train_data);
+  if (!ds->finished) ds->MarkFinished();     // bulk path: CreateFromMat + SetField, then straight to BoosterCreate
+  *out = new Booster(ds, parameters);
+  API_END();
+}
+
+int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished) {
+  API_BEGIN();
+  *is_finished = static_cast<Booster*>(handle)->UpdateOneIter() ? 1 : 0;
+  API_END();
+}
+
+int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished) {
+  API_BEGIN();
+  *is_finished = static_cast<Booster*>(handle)->UpdateOneIterCustom(grad, hess) ? 1 : 0;
+  API_END();
+}
+
+int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->ResetParameter(parameters);
+  API_END();
+}
+
+int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration, int feature_importance_type,
+                                  int64_t buffer_len, int64_t* out_len, char* out_str) {
+  API_BEGIN();
+  (void)feature_importance_type;
+  const std::string s = static_cast<Booster*>(handle)->SaveModelToString(start_iteration, num_iteration);
+  *out_len = static_cast<int64_t>(s.size()) + 1;
+  if (*out_len <= buffer_len) memcpy(out_str, s.c_str(), *out_len);
+  API_END();
+}
+
+int LGBM_BoosterGetNumClasses(BoosterHandle, int* out_len) { API_BEGIN(); *out_len = 1; API_END(); }
+int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->train()->num_total_features; API_END(); }
+int LGBM_BoosterNumModelPerIteration(BoosterHandle, int* out) { API_BEGIN(); *out = 1; API_END(); }
+int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->NumTrees(); API_END(); }
+int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->CurrentIteration(); API_END(); }
+
+int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  LGB_CHECK(data_idx == 0, "LGBM_BoosterGetPredict: only the training data (data_idx 0) is available");
+  auto b = static_cast<Booster*>(handle);
+  *out_len = b->train()->num_data;
+  b->CopyScores(out_result);
+  API_END();
+}
+
+int LGBM_BoosterFree(BoosterHandle handle) { API_BEGIN(); delete static_cast<Booster*>(handle); API_END(); }
+
+int LGBM_NetworkInit(const char* machines, int local_listen_port, int listen_time_out, int num_machines) {
+  API_BEGIN();
+  Network::Get()->Init(machines, local_listen_port, listen_time_out, num_machines);
+  API_END();
+}
+
+int LGBM_NetworkFree(void) { API_BEGIN(); Network::Get()->Free(); API_END(); }
+
+// ------------------------------------------------------------------------------------------------ extensions
+int LGBM_B200_DatasetGetFeatureInfo(DatasetHandle handle, int feature, int* num_bin, int* missing_type, int* default_bin,
+                                    int* most_freq_bin, int* is_trivial, double* min_val, double* max_val) {
+  API_BEGIN();
+  const BinMapperH& m = static_cast<Dataset*>(handle)->mappers.at(feature);
+  *num_bin = m.num_bin; *missing_type = m.missing_type; *default_bin = m.default_bin; *most_freq_bin = m.most_freq_bin;
+  *is_trivial = m.is_trivial; *min_val = m.min_val; *max_val = m.max_val;
+  API_END();
+}
+int LGBM_B200_DatasetGetBinUpperBounds(DatasetHandle handle, int feature, double* out) {
+  API_BEGIN();
+  const BinMapperH& m = static_cast<Dataset*>(handle)->mappers.at(feature);
+  for (int i = 0; i < m.num_bin; ++i) out[i] = m.upper[i];
+  API_END();
+}
+int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<Dataset*>(handle)->num_features(); API_END(); }
+int LGBM_B200_DatasetCopyBinColumn(DatasetHandle handle, int inner_feature, uint8_t* out) {
+  API_BEGIN();
+  static_cast<Dataset*>(handle)->CopyBinColumn(inner_feature, out);
+  API_END();
+}
+int LGBM_B200_DatasetCopyRowMajor(DatasetHandle handle, int64_t row, int64_t nrows, int* out_stride, uint8_t* out) {
+  API_BEGIN();
+  auto ds = static_cast<Dataset*>(handle);
+  *out_stride = ds->layout.rm_stride;
+  if (out != nullptr) ds->CopyRowMajor(row, nrows, out);
+  API_END();
+}
+int LGBM_B200_BoosterGetGradients(BoosterHandle handle, float* grad, float* hess) { API_BEGIN(); static_cast<Booster*>(handle)->CopyGradients(grad, hess); API_END(); }
+int LGBM_B200_BoosterGetQuantGradients(BoosterHandle handle, int8_t* grad, int8_t* hess, double* scales) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->CopyQuantGradients(grad, hess, scales);
+  API_END();
+}
+int LGBM_B200_BoosterRootHistogram(BoosterHandle handle, int64_t* out) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->DebugRootHistogram(reinterpret_cast<long long*>(out));
+  API_END();
+}
+int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float* out_ms) {
+  API_BEGIN();
+  *out_ms = static_cast<Booster*>(handle)->TimeRootHistogram(repeats);
+  API_END();
+}
+int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable) { API_BEGIN(); static_cast<Booster*>(handle)->EnableHistTiming(enable != 0); API_END(); }
+int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches) {
+  API_BEGIN();
+  auto b = static_cast<Booster*>(handle);
+  *hist_rows_visited = b->last_hist_rows_visited(); *hist_ms = b->last_hist_ms(); *kernel_launches = b->launches();
+  API_END();
+}
+int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->PredictRaw(data, nrow, ncol, out);
+  API_END();
+}
+
+}  // extern "C"

@@ -1,0 +1,50 @@
+// Parameter string ("k=v k=v ...") -> Config.  This is the native end of the strings the reference builds at
+// lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/params/BaseTrainParams.scala:25-40 (booster) and
+// lightgbm/.../LightGBMBase.scala:374-386 (dataset).  First occurrence of a key wins, which is what makes the reference's
+// passThroughArgs override explicit setters (core/.../utils/ParamsStringBuilder.scala:100-109).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+namespace lgb {
+
+struct Config {
+  std::string objective = "regression";
+  std::string boosting = "gbdt";
+  std::string tree_learner = "serial";
+  int num_iterations = 100;
+  double learning_rate = 0.1;
+  int num_leaves = 31;
+  int max_depth = -1;
+  int max_bin = 255;
+  int min_data_in_bin = 3;
+  int bin_construct_sample_cnt = 200000;
+  int min_data_in_leaf = 20;
+  double min_sum_hessian_in_leaf = 1e-3;
+  double lambda_l1 = 0.0, lambda_l2 = 0.0, min_gain_to_split = 0.0, max_delta_step = 0.0;
+  bool boost_from_average = true;
+  double sigmoid = 1.0;
+  bool is_unbalance = false;
+  double scale_pos_weight = 1.0;
+  bool use_missing = true, zero_as_missing = false, feature_pre_filter = true;
+  bool use_quantized_grad = false;
+  int num_grad_quant_bins = 4;
+  bool stochastic_rounding = true;
+  bool quant_train_renew_leaf = false;
+  int seed = 0;
+  int num_machines = 1;
+  int num_threads = 0;
+  int verbosity = 1;
+  int lambdarank_truncation_level = 30;
+  bool lambdarank_norm = true;
+  std::vector<double> label_gain;
+  std::vector<int> eval_at;
+  std::vector<int> categorical_feature;
+  std::map<std::string, std::string> raw;   // canonical key -> value as received (echoed into the model's parameters block)
+
+  void Set(const std::string& params);      // merges; keys already present in `params` earlier win over later ones
+  static std::string CanonicalKey(const std::string& k);
+};
+
+}  // namespace lgb

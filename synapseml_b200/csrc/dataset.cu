@@ -1,0 +1,727 @@
+// K1 (bin-boundary search on the sampled rows) and K2 (row binning) kernels + the Dataset host object.
+// Algorithm specification: upstream BinMapper::FindBin / FindBinWithZeroAsOneBin / GreedyFindBin / ValueToBin and
+// DatasetLoader::ConstructFromSampleData.  Reference call sites are listed in dataset.h.
+#include "dataset.h"
+
+#include <cub/device/device_segmented_radix_sort.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace lgb {
+
+int g_verbosity = 1;
+
+int ResolveDevice(const Config& cfg) {
+  auto it = cfg.raw.find("gpu_device_id");
+  if (it != cfg.raw.end()) {
+    int d = atoi(it->second.c_str());
+    if (d >= 0) return d;
+  }
+  // one process per GPU under torchrun: LOCAL_RANK names this process's device
+  const char* lr = getenv("LOCAL_RANK");
+  int ndev = 0;
+  LGB_CUDA(cudaGetDeviceCount(&ndev));
+  LGB_CHECK(ndev > 0, "No CUDA device is visible: this library has no CPU path");
+  if (lr != nullptr) return atoi(lr) % ndev;
+  return 0;
+}
+
+// =====================================================================================================================
+// K1: bin-boundary search.
+//   K1a  canonicalise NaNs + count them, then CUB segmented radix sort of every feature's sampled non-zero values
+//   K1b/c one thread per feature: distinct values + counts (with the implicit zero count), zero-as-one-bin split, greedy
+//        equal-frequency sweep with big-count values pinned, cnt_in_bin, trivial-feature filter, default/most-freq bin.
+// The sweep is inherently sequential per feature; parallelism is F.  It runs once per fit on <= 200k x F values.
+// =====================================================================================================================
+
+struct K1Params {
+  int max_bin, min_data_in_bin, filter_cnt, pre_filter, use_missing, zero_as_missing, total_sample_cnt;
+  int bstride;   // doubles per feature in the bounds / scratch arrays (>= max_bin + 2)
+};
+
+struct K1Meta {
+  int num_bin, missing_type, is_trivial, default_bin, most_freq_bin, pad;
+  double sparse_rate, min_val, max_val;
+};
+
+__global__ void k1_canon_nan(double* vals, const long long* seg_off, int* na_cnt, int nfeat) {
+  const int f = blockIdx.y;
+  if (f >= nfeat) return;
+  const long long b = seg_off[f], e = seg_off[f + 1];
+  int local = 0;
+  for (long long i = b + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
+    double v = vals[i];
+    if (v != v) { vals[i] = __longlong_as_double(0x7ff8000000000000LL); ++local; }   // +qNaN sorts after +inf in radix order
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_down_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0 && local) atomicAdd(&na_cnt[f], local);
+}
+
+__device__ __forceinline__ double UpperBoundOf(double a) { return nextafter(a, __longlong_as_double(0x7ff0000000000000LL)); }
+__device__ __forceinline__ bool EqualOrdered(double a, double b) { return b <= UpperBoundOf(a); }
+#define K1_ZERO_THRESHOLD ((double)1e-35f)
+#define K1_INF __longlong_as_double(0x7ff0000000000000LL)
+
+// Greedy equal-frequency bins over distinct values dv[0..nd) with counts cnt[]; writes bounds to out, returns how many.
+__device__ int K1Greedy(const double* dv, const int* cnt, int nd, int max_bin, long long total_cnt, int min_data_in_bin,
+                        double* out, double* upper, double* lower) {
+  int nb = 0;
+  if (nd <= max_bin) {
+    int cur = 0;
+    for (int i = 0; i < nd - 1; ++i) {
+      cur += cnt[i];
+      if (cur >= min_data_in_bin) {
+        double val = UpperBoundOf((dv[i] + dv[i + 1]) / 2.0);
+        if (nb == 0 || !EqualOrdered(out[nb - 1], val)) { out[nb++] = val; cur = 0; }
+      }
+    }
+    out[nb++] = K1_INF;
+    return nb;
+  }
+  if (min_data_in_bin > 0) {
+    int cap = (int)(total_cnt / min_data_in_bin);
+    if (cap < max_bin) max_bin = cap;
+    if (max_bin < 1) max_bin = 1;
+  }
+  const double mean0 = (double)total_cnt / max_bin;
+  int rest_bin_cnt = max_bin;
+  int rest_sample_cnt = (int)total_cnt;
+  for (int i = 0; i < nd; ++i) {
+    if (cnt[i] >= mean0) { --rest_bin_cnt; rest_sample_cnt -= cnt[i]; }
+  }
+  double mean_bin_size = (double)rest_sample_cnt / rest_bin_cnt;
+  for (int i = 0; i < max_bin; ++i) { upper[i] = K1_INF; lower[i] = K1_INF; }
+  int bin_cnt = 0;
+  lower[0] = dv[0];
+  int cur = 0;
+  for (int i = 0; i < nd - 1; ++i) {
+    const bool big_i = cnt[i] >= mean0;
+    const bool big_n = cnt[i + 1] >= mean0;
+    if (!big_i) rest_sample_cnt -= cnt[i];
+    cur += cnt[i];
+    double half = mean_bin_size * 0.5f;
+    if (half < 1.0) half = 1.0;
+    if (big_i || cur >= mean_bin_size || (big_n && cur >= half)) {
+      upper[bin_cnt] = dv[i];
+      ++bin_cnt;
+      lower[bin_cnt] = dv[i + 1];
+      if (bin_cnt >= max_bin - 1) break;
+      cur = 0;
+      if (!big_i) { --rest_bin_cnt; mean_bin_size = rest_sample_cnt / (double)rest_bin_cnt; }
+    }
+  }
+  ++bin_cnt;
+  for (int i = 0; i < bin_cnt - 1; ++i) {
+    double val = UpperBoundOf((upper[i] + lower[i + 1]) / 2.0);
+    if (nb == 0 || !EqualOrdered(out[nb - 1], val)) out[nb++] = val;
+  }
+  out[nb++] = K1_INF;
+  return nb;
+}
+
+__device__ int K1ZeroAsOneBin(const double* dv, const int* cnt, int nd, int max_bin, long long total_sample_cnt,
+                              int min_data_in_bin, double* out, double* tmp, double* upper, double* lower) {
+  int left_cnt_data = 0, cnt_zero = 0, right_cnt_data = 0;
+  for (int i = 0; i < nd; ++i) {
+    if (dv[i] <= -K1_ZERO_THRESHOLD) left_cnt_data += cnt[i];
+    else if (dv[i] > K1_ZERO_THRESHOLD) right_cnt_data += cnt[i];
+    else cnt_zero += cnt[i];
+  }
+  int left_cnt = -1;
+  for (int i = 0; i < nd; ++i) if (dv[i] > -K1_ZERO_THRESHOLD) { left_cnt = i; break; }
+  if (left_cnt < 0) left_cnt = nd;
+  int nb = 0;
+  if (left_cnt > 0 && max_bin > 1) {
+    int left_max_bin = (int)((double)left_cnt_data / (double)(total_sample_cnt - cnt_zero) * (max_bin - 1));
+    if (left_max_bin < 1) left_max_bin = 1;
+    nb = K1Greedy(dv, cnt, left_cnt, left_max_bin, left_cnt_data, min_data_in_bin, out, upper, lower);
+    if (nb > 0) out[nb - 1] = -K1_ZERO_THRESHOLD;
+  }
+  int right_start = -1;
+  for (int i = left_cnt; i < nd; ++i) if (dv[i] > K1_ZERO_THRESHOLD) { right_start = i; break; }
+  const int right_max_bin = max_bin - 1 - nb;
+  if (right_start >= 0 && right_max_bin > 0) {
+    int nr = K1Greedy(dv + right_start, cnt + right_start, nd - right_start, right_max_bin, right_cnt_data, min_data_in_bin,
+                      tmp, upper, lower);
+    out[nb++] = K1_ZERO_THRESHOLD;
+    for (int i = 0; i < nr; ++i) out[nb++] = tmp[i];
+  } else {
+    out[nb++] = K1_INF;
+  }
+  return nb;
+}
+
+__device__ int K1ValueToBin(double value, const double* bounds, int num_bin, int missing_type) {
+  if (value != value) {
+    if (missing_type == kMissingNaN) return num_bin - 1;
+    value = 0.0;
+  }
+  int l = 0, r = num_bin - 1;
+  if (missing_type == kMissingNaN) r -= 1;
+  while (l < r) {
+    int m = (r + l - 1) / 2;
+    if (value <= bounds[m]) r = m; else l = m + 1;
+  }
+  return l;
+}
+
+// sorted: every feature's segment sorted ascending, NaNs last.  distinct/counts: scratch with room for n_f + 2 per feature
+// (offset seg_off[f] + 2 f).  bounds/tmp/upper/lower/cib: [F][bstride].
+__global__ void k1_find_bin(const double* sorted, const long long* seg_off, const int* na_cnt_arr, int nfeat, K1Params p,
+                            double* distinct, int* counts, double* bounds, double* tmp, double* upper, double* lower,
+                            int* cib, K1Meta* meta) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= nfeat) return;
+  const double* v = sorted + seg_off[f];
+  const int n_all = (int)(seg_off[f + 1] - seg_off[f]);
+  int na_cnt = na_cnt_arr[f];
+  const int nv = n_all - na_cnt;       // non-NaN values
+  int missing_type;
+  if (!p.use_missing) missing_type = kMissingNone;
+  else if (p.zero_as_missing) missing_type = kMissingZero;
+  else if (na_cnt == 0) missing_type = kMissingNone;
+  else missing_type = kMissingNaN;
+  if (missing_type != kMissingNaN) na_cnt = 0;
+  const int zero_cnt = p.total_sample_cnt - nv - na_cnt;
+  double* dv = distinct + seg_off[f] + 2LL * f;
+  int* dc = counts + seg_off[f] + 2LL * f;
+  int nd = 0;
+  if (nv == 0 || (v[0] > 0.0 && zero_cnt > 0)) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
+  if (nv > 0) { dv[nd] = v[0]; dc[nd] = 1; ++nd; }
+  for (int i = 1; i < nv; ++i) {
+    const double a = v[i - 1], b = v[i];
+    if (!EqualOrdered(a, b)) {
+      if (a < 0.0 && b > 0.0) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
+      dv[nd] = b; dc[nd] = 1; ++nd;
+    } else {
+      dv[nd - 1] = b;
+      ++dc[nd - 1];
+    }
+  }
+  if (nv > 0 && v[nv - 1] < 0.0 && zero_cnt > 0) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
+  K1Meta m;
+  m.min_val = dv[0];
+  m.max_val = dv[nd - 1];
+  double* out = bounds + (long long)f * p.bstride;
+  double* t = tmp + (long long)f * p.bstride;
+  double* up = upper + (long long)f * p.bstride;
+  double* lo = lower + (long long)f * p.bstride;
+  int num_bin;
+  if (missing_type == kMissingZero) {
+    num_bin = K1ZeroAsOneBin(dv, dc, nd, p.max_bin, p.total_sample_cnt, p.min_data_in_bin, out, t, up, lo);
+    if (num_bin == 2) missing_type = kMissingNone;
+  } else if (missing_type == kMissingNone) {
+    num_bin = K1ZeroAsOneBin(dv, dc, nd, p.max_bin, p.total_sample_cnt, p.min_data_in_bin, out, t, up, lo);
+  } else {
+    num_bin = K1ZeroAsOneBin(dv, dc, nd, p.max_bin - 1, p.total_sample_cnt - na_cnt, p.min_data_in_bin, out, t, up, lo);
+    out[num_bin++] = __longlong_as_double(0x7ff8000000000000LL);
+  }
+  int* c = cib + (long long)f * p.bstride;
+  for (int i = 0; i < num_bin; ++i) c[i] = 0;
+  {
+    int i_bin = 0;
+    for (int i = 0; i < nd; ++i) {
+      while (dv[i] > out[i_bin] && i_bin < num_bin - 1) ++i_bin;
+      c[i_bin] += dc[i];
+    }
+    if (missing_type == kMissingNaN) c[num_bin - 1] = na_cnt;
+  }
+  int is_trivial = num_bin <= 1;
+  if (!is_trivial && p.pre_filter) {
+    bool need = true;
+    int sum_left = 0;
+    for (int i = 0; i + 1 < num_bin; ++i) {
+      sum_left += c[i];
+      if (sum_left >= p.filter_cnt && p.total_sample_cnt - sum_left >= p.filter_cnt) { need = false; break; }
+    }
+    if (need) is_trivial = 1;
+  }
+  m.num_bin = num_bin;
+  m.missing_type = missing_type;
+  m.is_trivial = is_trivial;
+  m.default_bin = 0;
+  m.most_freq_bin = 0;
+  m.sparse_rate = 1.0;
+  if (!is_trivial) {
+    m.default_bin = K1ValueToBin(0.0, out, num_bin, missing_type);
+    int arg = 0;
+    for (int i = 1; i < num_bin; ++i) if (c[i] > c[arg]) arg = i;
+    const double max_sparse_rate = (double)c[arg] / p.total_sample_cnt;
+    if (arg != m.default_bin && max_sparse_rate < 0.7) arg = m.default_bin;
+    m.most_freq_bin = arg;
+    m.sparse_rate = (double)c[arg] / p.total_sample_cnt;
+  }
+  m.pad = 0;
+  meta[f] = m;
+}
+
+// =====================================================================================================================
+// K2: row binning.  One CTA owns a 32-feature tile and walks 128-row blocks (aligned to absolute row numbers so that
+// the column-major stores are 16-byte aligned).  The tile's bin boundaries sit in shared memory (stride 257 doubles to
+// spread banks); lanes map to features so a warp reads 32 consecutive doubles of one input row; bins go to two shared
+// tiles which are then written out with 128-bit stores: column-major (16 rows of one feature per store) and row-major
+// (16 features of one row per store).
+// Algorithmic bytes: N * F * (8 read + 1 write) (+1 for the second layout).
+// =====================================================================================================================
+
+constexpr int K2_ROWS = 128;
+constexpr int K2_FT = 32;
+constexpr int K2_BSTRIDE = 257;
+
+__global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ data, int nrow, int ncol, long long start_row,
+                                                   const double* __restrict__ bounds, const FeatureMetaDev* __restrict__ fmeta,
+                                                   int f_used, uint8_t* __restrict__ cm, long long n_pad,
+                                                   uint8_t* __restrict__ rm, int rm_stride) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* sb = reinterpret_cast<double*>(smem_raw);                               // [32][257]
+  uint8_t* tile_cm = smem_raw + sizeof(double) * K2_FT * K2_BSTRIDE;               // [32][128]
+  uint8_t* tile_rm = tile_cm + K2_FT * K2_ROWS;                                    // [128][32]
+  const int ft = blockIdx.y;
+  const int f0 = ft * K2_FT;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < K2_FT * kMaxBinsPerFeature; i += blockDim.x) {
+    int f = i >> 8, b = i & 255;
+    sb[f * K2_BSTRIDE + b] = (f0 + f < f_used) ? bounds[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0.0;
+  }
+  const int fi = f0 + lane;
+  int num_bin = 1, missing_type = 0, real = 0;
+  if (fi < f_used) { num_bin = fmeta[fi].num_bin; missing_type = fmeta[fi].missing_type; real = fmeta[fi].real_index; }
+  __syncthreads();
+  const long long first_blk = start_row / K2_ROWS;
+  const long long last_blk = (start_row + nrow - 1) / K2_ROWS;
+  const double* myb = sb + lane * K2_BSTRIDE;
+  for (long long blk = first_blk + blockIdx.x; blk <= last_blk; blk += gridDim.x) {
+    const long long r0 = blk * K2_ROWS;
+    // 8 warps x 16 rows
+    #pragma unroll 4
+    for (int k = 0; k < 16; ++k) {
+      const int rr = warp * 16 + k;
+      const long long row = r0 + rr;
+      int bin = 0;
+      if (fi < f_used && row >= start_row && row < start_row + nrow) {
+        double value = data[(row - start_row) * (long long)ncol + real];
+        if (value != value) {
+          if (missing_type == kMissingNaN) { bin = num_bin - 1; goto done; }
+          value = 0.0;
+        }
+        {
+          int l = 0, r = num_bin - 1;
+          if (missing_type == kMissingNaN) r -= 1;
+          while (l < r) {
+            const int m = (r + l - 1) >> 1;
+            if (value <= myb[m]) r = m; else l = m + 1;
+          }
+          bin = l;
+        }
+      }
+    done:
+      tile_cm[lane * K2_ROWS + rr] = (uint8_t)bin;
+      tile_rm[rr * K2_FT + lane] = (uint8_t)bin;
+    }
+    __syncthreads();
+    const bool full = (r0 >= start_row) && (r0 + K2_ROWS <= start_row + nrow);
+    {  // column-major: thread -> (feature, 16-row chunk)
+      const int f = threadIdx.x >> 3, ch = threadIdx.x & 7;
+      if (f0 + f < f_used) {
+        uint8_t* dst = cm + (long long)(f0 + f) * n_pad + r0 + ch * 16;
+        const uint8_t* src = tile_cm + f * K2_ROWS + ch * 16;
+        if (full) {
+          *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+        } else {
+          for (int j = 0; j < 16; ++j) {
+            long long row = r0 + ch * 16 + j;
+            if (row >= start_row && row < start_row + nrow) dst[j] = src[j];
+          }
+        }
+      }
+    }
+    {  // row-major: thread -> (row, 16-feature half)
+      const int rr = threadIdx.x >> 1, half = threadIdx.x & 1;
+      const long long row = r0 + rr;
+      if (row >= start_row && row < start_row + nrow) {
+        uint8_t* dst = rm + row * (long long)rm_stride + f0 + half * 16;
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(tile_rm + rr * K2_FT + half * 16);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// =====================================================================================================================
+// Host side
+// =====================================================================================================================
+
+static BinLayout ChooseLayout(int f_used) {
+  BinLayout L;
+  if (f_used <= 32) { L.rows_per_step = 4; L.rm_stride = 32; }
+  else if (f_used <= 64) { L.rows_per_step = 2; L.rm_stride = 64; }
+  else { L.rows_per_step = 1; L.rm_stride = RoundUp(f_used, 128); }
+  L.tile_features_q = 32 / L.rows_per_step * 4;
+  L.tile_features_f = 32 / L.rows_per_step * 2;
+  return L;
+}
+
+Dataset::~Dataset() { FreeSlots(); }
+
+void Dataset::FinishSchema() {
+  used.clear();
+  real_to_inner.assign(num_total_features, -1);
+  max_num_bin = 1;
+  for (int j = 0; j < num_total_features; ++j) {
+    if (!mappers[j].is_trivial) {
+      real_to_inner[j] = static_cast<int>(used.size());
+      used.push_back(j);
+      max_num_bin = std::max(max_num_bin, mappers[j].num_bin);
+    }
+  }
+  LGB_CHECK(max_num_bin <= kMaxBinsPerFeature,
+            "A feature has %d bins; only uint8 bin storage (<= %d bins, max_bin <= 255) is built in this version",
+            max_num_bin, kMaxBinsPerFeature);
+  if (feature_names.empty())
+    for (int j = 0; j < num_total_features; ++j) feature_names.push_back("Column_" + std::to_string(j));
+  const int F = num_features();
+  layout = ChooseLayout(std::max(F, 1));
+  std::vector<double> hb(static_cast<size_t>(std::max(F, 1)) * kMaxBinsPerFeature, std::numeric_limits<double>::infinity());
+  std::vector<FeatureMetaDev> hm(std::max(F, 1));
+  std::vector<int> hr(std::max(F, 1), 0);
+  for (int i = 0; i < F; ++i) {
+    const BinMapperH& m = mappers[used[i]];
+    for (int b = 0; b < m.num_bin; ++b) hb[static_cast<size_t>(i) * kMaxBinsPerFeature + b] = m.upper[b];
+    hm[i] = FeatureMetaDev{m.num_bin, m.missing_type, m.default_bin, m.most_freq_bin, used[i], {0, 0, 0}};
+    hr[i] = used[i];
+  }
+  LGB_CUDA(cudaSetDevice(device));
+  d_bounds.Alloc(hb.size());
+  LGB_CUDA(cudaMemcpy(d_bounds.p, hb.data(), hb.size() * sizeof(double), cudaMemcpyHostToDevice));
+  d_fmeta.Alloc(hm.size());
+  LGB_CUDA(cudaMemcpy(d_fmeta.p, hm.data(), hm.size() * sizeof(FeatureMetaDev), cudaMemcpyHostToDevice));
+  d_real_index.Alloc(hr.size());
+  LGB_CUDA(cudaMemcpy(d_real_index.p, hr.data(), hr.size() * sizeof(int), cudaMemcpyHostToDevice));
+}
+
+void Dataset::AllocateRows(int64_t n) {
+  LGB_CHECK(n >= 0 && n < (int64_t(1) << 31) - 256, "num_data %lld out of range", (long long)n);
+  num_data = n;
+  n_pad = RoundUp<int64_t>(std::max<int64_t>(n, 1), 128);
+  LGB_CUDA(cudaSetDevice(device));
+  const int F = std::max(num_features(), 1);
+  d_cm.AllocZero(static_cast<size_t>(F) * n_pad);
+  d_rm.AllocZero(static_cast<size_t>(n_pad) * layout.rm_stride);
+  label.assign(n, 0.0f);
+  pushed_rows = 0;
+  finished = false;
+}
+
+Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_indices, int32_t ncol, const int* num_per_col,
+                                          int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
+                                          const char* params) {
+  (void)sample_indices;
+  std::unique_ptr<Dataset> ds(new Dataset());
+  ds->param_string = params ? params : "";
+  ds->cfg.Set(ds->param_string);
+  g_verbosity = ds->cfg.verbosity;
+  const Config& c = ds->cfg;
+  LGB_CHECK(ncol > 0, "ncol must be positive");
+  LGB_CHECK(c.max_bin >= 2 && c.max_bin <= 255, "max_bin=%d is outside [2, 255] (uint8 bin storage)", c.max_bin);
+  LGB_CHECK(c.categorical_feature.empty(), "categorical_feature is not supported by this library yet");
+  LGB_CHECK(!c.zero_as_missing, "zero_as_missing=true is not supported by this library yet");
+  ds->device = ResolveDevice(c);
+  LGB_CUDA(cudaSetDevice(ds->device));
+  ds->num_total_features = ncol;
+  // ---- stage the column-major non-zero sample (SampledData.scala:30-40) into one device array
+  std::vector<long long> off(ncol + 1, 0);
+  for (int j = 0; j < ncol; ++j) {
+    LGB_CHECK(num_per_col[j] >= 0 && num_per_col[j] <= num_sample_row, "num_per_col[%d]=%d out of range", j, num_per_col[j]);
+    off[j + 1] = off[j] + num_per_col[j];
+  }
+  const long long total = off[ncol];
+  DevBuf<double> d_vals, d_sorted, d_distinct, d_bnd, d_tmp, d_up, d_lo;
+  DevBuf<long long> d_off;
+  DevBuf<int> d_na, d_counts, d_cib;
+  DevBuf<K1Meta> d_meta;
+  d_vals.Alloc(std::max<long long>(total, 1));
+  d_sorted.Alloc(std::max<long long>(total, 1));
+  for (int j = 0; j < ncol; ++j)
+    if (num_per_col[j] > 0)
+      LGB_CUDA(cudaMemcpy(d_vals.p + off[j], sample_data[j], sizeof(double) * num_per_col[j], cudaMemcpyHostToDevice));
+  d_off.Alloc(ncol + 1);
+  LGB_CUDA(cudaMemcpy(d_off.p, off.data(), sizeof(long long) * (ncol + 1), cudaMemcpyHostToDevice));
+  d_na.AllocZero(ncol);
+  if (total > 0) {
+    dim3 grid(static_cast<unsigned>(std::min<long long>(CeilDiv<long long>(num_sample_row, 256), 64)), ncol);
+    k1_canon_nan<<<grid, 256>>>(d_vals.p, d_off.p, d_na.p, ncol);
+    LGB_CUDA(cudaGetLastError());
+    size_t tmp_bytes = 0;
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortKeys(nullptr, tmp_bytes, d_vals.p, d_sorted.p, total, ncol, d_off.p, d_off.p + 1));
+    DevBuf<unsigned char> d_cubtmp;
+    d_cubtmp.Alloc(std::max<size_t>(tmp_bytes, 16));
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortKeys(d_cubtmp.p, tmp_bytes, d_vals.p, d_sorted.p, total, ncol, d_off.p, d_off.p + 1));
+  }
+  K1Params p;
+  p.max_bin = c.max_bin;
+  p.min_data_in_bin = c.min_data_in_bin;
+  // filter_cnt: the reference passes num_local_row = 1 and num_dist_row = N (ReferenceDatasetUtils.scala:44-45)
+  const int64_t denom = num_dist_row > 0 ? num_dist_row : std::max<int64_t>(num_local_row, 1);
+  p.filter_cnt = static_cast<int>(static_cast<double>(static_cast<size_t>(c.min_data_in_leaf) * static_cast<size_t>(num_sample_row)) / denom);
+  p.pre_filter = c.feature_pre_filter;
+  p.use_missing = c.use_missing;
+  p.zero_as_missing = c.zero_as_missing;
+  p.total_sample_cnt = num_sample_row;
+  p.bstride = c.max_bin + 4;
+  d_distinct.Alloc(total + 2LL * ncol + 2);
+  d_counts.Alloc(total + 2LL * ncol + 2);
+  const size_t bs = static_cast<size_t>(ncol) * p.bstride;
+  d_bnd.Alloc(bs); d_tmp.Alloc(bs); d_up.Alloc(bs); d_lo.Alloc(bs); d_cib.Alloc(bs);
+  d_meta.Alloc(ncol);
+  k1_find_bin<<<CeilDiv(ncol, 32), 32>>>(d_sorted.p, d_off.p, d_na.p, ncol, p, d_distinct.p, d_counts.p, d_bnd.p, d_tmp.p,
+                                         d_up.p, d_lo.p, d_cib.p, d_meta.p);
+  LGB_CUDA(cudaGetLastError());
+  LGB_CUDA(cudaDeviceSynchronize());
+  std::vector<K1Meta> hmeta(ncol);
+  std::vector<double> hb(bs);
+  LGB_CUDA(cudaMemcpy(hmeta.data(), d_meta.p, sizeof(K1Meta) * ncol, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(hb.data(), d_bnd.p, sizeof(double) * bs, cudaMemcpyDeviceToHost));
+  ds->mappers.resize(ncol);
+  for (int j = 0; j < ncol; ++j) {
+    BinMapperH& m = ds->mappers[j];
+    m.num_bin = hmeta[j].num_bin; m.missing_type = hmeta[j].missing_type; m.is_trivial = hmeta[j].is_trivial;
+    m.default_bin = hmeta[j].default_bin; m.most_freq_bin = hmeta[j].most_freq_bin; m.sparse_rate = hmeta[j].sparse_rate;
+    m.min_val = hmeta[j].min_val; m.max_val = hmeta[j].max_val;
+    m.upper.assign(hb.begin() + static_cast<size_t>(j) * p.bstride, hb.begin() + static_cast<size_t>(j) * p.bstride + m.num_bin);
+  }
+  ds->FinishSchema();
+  ds->AllocateRows(num_local_row);
+  return ds.release();
+}
+
+// ---- reference dataset serialisation: the byte[] the Scala side ships driver -> executors is opaque to it
+// (ReferenceDatasetUtils.scala:99-138), so the format is ours: little-endian, versioned.
+namespace {
+struct Writer {
+  std::string s;
+  template <typename T> void Put(const T& v) { s.append(reinterpret_cast<const char*>(&v), sizeof(T)); }
+  void PutStr(const std::string& v) { Put<int32_t>(static_cast<int32_t>(v.size())); s.append(v); }
+};
+struct Reader {
+  const char* p; const char* e;
+  template <typename T> T Get() { LGB_CHECK(p + sizeof(T) <= e, "Serialized reference dataset is truncated"); T v; memcpy(&v, p, sizeof(T)); p += sizeof(T); return v; }
+  std::string GetStr() { int32_t n = Get<int32_t>(); LGB_CHECK(n >= 0 && p + n <= e, "Serialized reference dataset is truncated"); std::string v(p, p + n); p += n; return v; }
+};
+constexpr uint32_t kRefMagic = 0x4C42B200u;
+}  // namespace
+
+std::string Dataset::SerializeReference() const {
+  Writer w;
+  w.Put<uint32_t>(kRefMagic);
+  w.Put<int32_t>(1);
+  w.PutStr(param_string);
+  w.Put<int32_t>(num_total_features);
+  for (const auto& m : mappers) {
+    w.Put<int32_t>(m.num_bin); w.Put<int32_t>(m.missing_type); w.Put<int32_t>(m.is_trivial); w.Put<int32_t>(m.default_bin);
+    w.Put<int32_t>(m.most_freq_bin); w.Put<double>(m.sparse_rate); w.Put<double>(m.min_val); w.Put<double>(m.max_val);
+    for (double b : m.upper) w.Put<double>(b);
+  }
+  for (const auto& n : feature_names) w.PutStr(n);
+  return w.s;
+}
+
+Dataset* Dataset::CreateFromSerializedReference(const void* buf, int32_t len, int64_t num_row, const char* params) {
+  Reader r{static_cast<const char*>(buf), static_cast<const char*>(buf) + len};
+  LGB_CHECK(r.Get<uint32_t>() == kRefMagic, "Buffer is not a serialized reference dataset of this library");
+  LGB_CHECK(r.Get<int32_t>() == 1, "Unsupported serialized reference dataset version");
+  std::unique_ptr<Dataset> ds(new Dataset());
+  ds->param_string = r.GetStr();
+  ds->cfg.Set(params ? params : "");     // params given here win, then the ones the reference was built with
+  ds->cfg.Set(ds->param_string);
+  g_verbosity = ds->cfg.verbosity;
+  ds->device = ResolveDevice(ds->cfg);
+  ds->num_total_features = r.Get<int32_t>();
+  LGB_CHECK(ds->num_total_features > 0 && ds->num_total_features < (1 << 24), "Corrupt serialized reference dataset");
+  ds->mappers.resize(ds->num_total_features);
+  for (auto& m : ds->mappers) {
+    m.num_bin = r.Get<int32_t>(); m.missing_type = r.Get<int32_t>(); m.is_trivial = r.Get<int32_t>();
+    m.default_bin = r.Get<int32_t>(); m.most_freq_bin = r.Get<int32_t>(); m.sparse_rate = r.Get<double>();
+    m.min_val = r.Get<double>(); m.max_val = r.Get<double>();
+    LGB_CHECK(m.num_bin >= 1 && m.num_bin <= 65536, "Corrupt serialized reference dataset");
+    m.upper.resize(m.num_bin);
+    for (auto& b : m.upper) b = r.Get<double>();
+  }
+  ds->feature_names.resize(ds->num_total_features);
+  for (auto& n : ds->feature_names) n = r.GetStr();
+  ds->FinishSchema();
+  ds->AllocateRows(num_row);
+  return ds.release();
+}
+
+Dataset* Dataset::CreateByReference(int64_t num_row) const {
+  std::unique_ptr<Dataset> ds(new Dataset());
+  ds->param_string = param_string;
+  ds->cfg = cfg;
+  ds->device = device;
+  ds->num_total_features = num_total_features;
+  ds->mappers = mappers;
+  ds->feature_names = feature_names;
+  ds->FinishSchema();
+  ds->AllocateRows(num_row);
+  return ds.release();
+}
+
+void Dataset::SetFeatureNames(const char** names, int n) {
+  LGB_CHECK(n == num_total_features, "Expected %d feature names, got %d", num_total_features, n);
+  feature_names.assign(names, names + n);
+}
+
+constexpr size_t kStageBytes = size_t(32) << 20;
+
+void Dataset::EnsureSlots(int n) {
+  std::lock_guard<std::mutex> g(mu_);
+  LGB_CUDA(cudaSetDevice(device));
+  while (static_cast<int>(slots_.size()) < n) {
+    PushSlot s;
+    s.cap_rows = std::max<size_t>(kStageBytes / (sizeof(double) * num_total_features), 1);
+    const size_t bytes = s.cap_rows * num_total_features * sizeof(double);
+    for (int k = 0; k < 2; ++k) {
+      LGB_CUDA(cudaMallocHost(&s.pinned[k], bytes));
+      LGB_CUDA(cudaMalloc(&s.dstage[k], bytes));
+      LGB_CUDA(cudaEventCreateWithFlags(&s.ev[k], cudaEventDisableTiming));
+    }
+    LGB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    slots_.push_back(s);
+  }
+}
+
+void Dataset::FreeSlots() {
+  cudaSetDevice(device);
+  for (auto& s : slots_) {
+    if (s.stream) cudaStreamSynchronize(s.stream);
+    for (int k = 0; k < 2; ++k) {
+      if (s.pinned[k]) cudaFreeHost(s.pinned[k]);
+      if (s.dstage[k]) cudaFree(s.dstage[k]);
+      if (s.ev[k]) cudaEventDestroy(s.ev[k]);
+    }
+    if (s.stream) cudaStreamDestroy(s.stream);
+  }
+  slots_.clear();
+}
+
+void Dataset::InitStreaming(bool has_w, bool has_init, bool has_q, int nclasses, int nthreads) {
+  LGB_CHECK(nclasses <= 1, "Multiclass init scores (nclasses=%d) are not supported by this library yet", nclasses);
+  has_weight = has_w; has_init_score = has_init; has_query = has_q;
+  if (has_w) weight.assign(num_data, 0.0f);
+  if (has_init) init_score.assign(num_data, 0.0);
+  if (has_q) query_id.assign(num_data, 0);
+  EnsureSlots(std::max(nthreads, 1));
+  streaming_inited = true;
+}
+
+void Dataset::FlushSlot(PushSlot* s) {
+  if (s->seg_rows == 0) return;
+  LGB_CUDA(cudaSetDevice(device));
+  const int k = s->cur;
+  const size_t bytes = static_cast<size_t>(s->seg_rows) * num_total_features * sizeof(double);
+  LGB_CUDA(cudaMemcpyAsync(s->dstage[k], s->pinned[k], bytes, cudaMemcpyHostToDevice, s->stream));
+  const int F = num_features();
+  if (F > 0) {
+    const long long nblk = (s->seg_start + s->seg_rows - 1) / K2_ROWS - s->seg_start / K2_ROWS + 1;
+    const int ftiles = CeilDiv(F, K2_FT);
+    dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
+    const size_t smem = sizeof(double) * K2_FT * K2_BSTRIDE + 2 * K2_FT * K2_ROWS;
+    static bool attr_set = false;
+    if (!attr_set) {
+      LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+      attr_set = true;
+    }
+    k2_bin_rows<<<grid, 256, smem, s->stream>>>(s->dstage[k], static_cast<int>(s->seg_rows), num_total_features, s->seg_start,
+                                                d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+    LGB_CUDA(cudaGetLastError());
+  }
+  LGB_CUDA(cudaEventRecord(s->ev[k], s->stream));
+  s->cur ^= 1;
+  LGB_CUDA(cudaEventSynchronize(s->ev[s->cur]));   // the buffer we are about to refill must have been consumed
+  s->seg_rows = 0;
+}
+
+void Dataset::PushRows(const void* data, int data_type, int32_t nrow, int32_t ncol, int64_t start_row, const float* lab,
+                       const float* w, const double* init, const int32_t* q, int tid) {
+  LGB_CHECK(data_type == 1 || data_type == 0, "PushRows: data_type must be C_API_DTYPE_FLOAT32 or FLOAT64");
+  LGB_CHECK(ncol == num_total_features, "PushRows: got %d columns, the dataset has %d features", ncol, num_total_features);
+  LGB_CHECK(nrow >= 0 && start_row >= 0 && start_row + nrow <= num_data, "PushRows: rows [%lld, %lld) are outside the dataset (%lld rows)",
+            (long long)start_row, (long long)(start_row + nrow), (long long)num_data);
+  LGB_CHECK(!finished, "PushRows: the dataset is already finished");
+  if (tid < 0) tid = 0;
+  if (static_cast<int>(slots_.size()) <= tid) EnsureSlots(tid + 1);
+  PushSlot* s = &slots_[tid];
+  int64_t done = 0;
+  while (done < nrow) {
+    if (s->seg_rows > 0 && (start_row + done != s->seg_start + s->seg_rows || static_cast<size_t>(s->seg_rows) >= s->cap_rows)) FlushSlot(s);
+    if (s->seg_rows == 0) s->seg_start = start_row + done;
+    const int64_t take = std::min<int64_t>(nrow - done, static_cast<int64_t>(s->cap_rows) - s->seg_rows);
+    double* dst = s->pinned[s->cur] + static_cast<size_t>(s->seg_rows) * ncol;
+    if (data_type == 1) {
+      memcpy(dst, static_cast<const double*>(data) + static_cast<size_t>(done) * ncol, sizeof(double) * take * ncol);
+    } else {
+      const float* src = static_cast<const float*>(data) + static_cast<size_t>(done) * ncol;
+      for (size_t i = 0; i < static_cast<size_t>(take) * ncol; ++i) dst[i] = src[i];
+    }
+    s->seg_rows += take;
+    done += take;
+  }
+  if (lab) std::copy(lab, lab + nrow, label.begin() + start_row);
+  if (w && has_weight) std::copy(w, w + nrow, weight.begin() + start_row);
+  if (init && has_init_score) std::copy(init, init + nrow, init_score.begin() + start_row);
+  if (q && has_query) std::copy(q, q + nrow, query_id.begin() + start_row);
+  bool all_in = false;
+  {
+    std::lock_guard<std::mutex> g(mu_);
+    pushed_rows += nrow;
+    all_in = pushed_rows >= num_data;
+  }
+  if (all_in && !wait_for_manual_finish) MarkFinished();
+}
+
+void Dataset::MarkFinished() {
+  if (finished) return;
+  LGB_CUDA(cudaSetDevice(device));
+  for (auto& s : slots_) FlushSlot(&s);
+  for (auto& s : slots_) LGB_CUDA(cudaStreamSynchronize(s.stream));
+  FreeSlots();
+  d_label.Alloc(std::max<int64_t>(num_data, 1));
+  LGB_CUDA(cudaMemcpy(d_label.p, label.data(), sizeof(float) * num_data, cudaMemcpyHostToDevice));
+  if (has_weight) {
+    d_weight.Alloc(std::max<int64_t>(num_data, 1));
+    LGB_CUDA(cudaMemcpy(d_weight.p, weight.data(), sizeof(float) * num_data, cudaMemcpyHostToDevice));
+  }
+  if (has_init_score) {
+    d_init_score.Alloc(std::max<int64_t>(num_data, 1));
+    LGB_CUDA(cudaMemcpy(d_init_score.p, init_score.data(), sizeof(double) * num_data, cudaMemcpyHostToDevice));
+  }
+  if (has_query && query_boundaries.empty()) {
+    // runs of equal consecutive group ids are queries (the streaming path pushes one id per row)
+    query_boundaries.push_back(0);
+    for (int64_t i = 1; i < num_data; ++i)
+      if (query_id[i] != query_id[i - 1]) query_boundaries.push_back(static_cast<int32_t>(i));
+    query_boundaries.push_back(static_cast<int32_t>(num_data));
+  }
+  if (!query_boundaries.empty()) {
+    d_query_boundaries.Alloc(query_boundaries.size());
+    LGB_CUDA(cudaMemcpy(d_query_boundaries.p, query_boundaries.data(), sizeof(int32_t) * query_boundaries.size(), cudaMemcpyHostToDevice));
+  }
+  finished = true;
+}
+
+void Dataset::CopyBinColumn(int inner_feature, uint8_t* out) const {
+  LGB_CHECK(inner_feature >= 0 && inner_feature < num_features(), "inner feature %d out of range", inner_feature);
+  LGB_CUDA(cudaSetDevice(device));
+  LGB_CUDA(cudaMemcpy(out, d_cm.p + static_cast<size_t>(inner_feature) * n_pad, num_data, cudaMemcpyDeviceToHost));
+}
+
+void Dataset::CopyRowMajor(int64_t row, int64_t nrows, uint8_t* out) const {
+  LGB_CHECK(row >= 0 && row + nrows <= num_data, "row range out of bounds");
+  LGB_CUDA(cudaSetDevice(device));
+  LGB_CUDA(cudaMemcpy(out, d_rm.p + static_cast<size_t>(row) * layout.rm_stride, static_cast<size_t>(nrows) * layout.rm_stride, cudaMemcpyDeviceToHost));
+}
+
+}  // namespace lgb

@@ -1,0 +1,965 @@
+// Device kernels of the training hot path (K3-K8).  Algorithm specification: SURVEY.md Appendix A.5-A.9 (upstream
+// objective / feature_histogram / data_partition / gbdt); the kernels are designed for sm_100a from that specification.
+//
+// Conventions
+//  * Histograms are exact integers in every mode.  Quantized mode accumulates the int8 (grad, hess) pairs; float mode
+//    first converts float32 grad/hess to 19-bit fixed point with power-of-two scales (one scale per iteration from
+//    max|g|, max|h|), so sums are order-independent: the result does not depend on the number of GPUs or on atomic
+//    ordering, and the int64 global histogram converts back to float exactly (scale is 2^k).
+//  * Global histogram entry = (int64 sum_g, int64 sum_h) per (feature, bin), 256 bin slots per feature.
+//  * All per-tree control flow lives in device memory (TreeCtrl / LeafDev) so a whole tree is enqueued with no host
+//    round trip; kernels return immediately once ctrl->done is set.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "booster.h"
+#include "softmath.cuh"
+
+namespace lgb {
+
+#define KEPS ((double)1e-15f)
+#define KMINSCORE (-__longlong_as_double(0x7ff0000000000000LL))
+constexpr int kBins = 256;
+constexpr int kFixBits = 19;                       // float mode: |fixed-point value| <= 2^19 per row
+constexpr int kFixRowsPerCopy = 4000;              // 4000 * 2^19 < 2^31
+constexpr int kHistThreads = 1024;
+constexpr int kHistMinRowsPerCta = 2048;
+constexpr int kPartBlocks = 592;                   // 4 x 148 SMs
+constexpr int kPartThreads = 256;
+
+__device__ __forceinline__ int RoundIntD(double x) { return static_cast<int>(x + 0.5f); }
+__device__ __forceinline__ int SignD(double x) { return (x > 0.0) - (x < 0.0); }
+
+// ------------------------------------------------------------------------------------------------ K3 gradients
+__global__ void k_grad_binary(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
+                              float* __restrict__ grad, float* __restrict__ hess, int n, double sigmoid, double lw_neg, double lw_pos) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int is_pos = label[i] > 0.0f;
+    const int lab = is_pos ? 1 : -1;
+    const double lw = is_pos ? lw_pos : lw_neg;
+    const double response = -lab * sigmoid / (1.0f + SoftExp(lab * sigmoid * score[i]));
+    const double abs_response = fabs(response);
+    if (weight == nullptr) {
+      grad[i] = static_cast<float>(response * lw);
+      hess[i] = static_cast<float>(abs_response * (sigmoid - abs_response) * lw);
+    } else {
+      grad[i] = static_cast<float>(response * lw * weight[i]);
+      hess[i] = static_cast<float>(abs_response * (sigmoid - abs_response) * lw * weight[i]);
+    }
+  }
+}
+
+__global__ void k_grad_l2(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
+                          float* __restrict__ grad, float* __restrict__ hess, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (weight == nullptr) {
+      grad[i] = static_cast<float>(score[i] - label[i]);
+      hess[i] = 1.0f;
+    } else {
+      grad[i] = static_cast<float>(static_cast<float>(score[i] - label[i]) * weight[i]);
+      hess[i] = static_cast<float>(weight[i]);
+    }
+  }
+}
+
+// LambdaRank-NDCG.  One CTA per query.  Step 1: stable rank of every document by score (descending) by counting, which
+// equals std::stable_sort's order.  Step 2: one thread per document replays exactly the pairs that touch it, in the
+// CPU's (i, j) order, so its float32 lambda/hessian sums are bit-identical to the sequential loop.  Step 3: thread 0
+// re-walks the pairs in (i, j) order for the double-precision sum_lambdas (needed for the log2 normalisation).
+struct LambdarankArgs {
+  const double* score; const float* label; const float* weight; const int* qb;
+  const double* inv_max_dcg; const double* label_gain; const double* discount; const double* sigmoid_table;
+  float* grad; float* hess;
+  double sigmoid, min_sigmoid_input, max_sigmoid_input, idx_factor;
+  int truncation_level, norm, table_size, max_cnt;
+};
+
+__device__ __forceinline__ double LrSigmoid(const LambdarankArgs& a, double s) {
+  if (s <= a.min_sigmoid_input) return a.sigmoid_table[0];
+  if (s >= a.max_sigmoid_input) return a.sigmoid_table[a.table_size - 1];
+  return a.sigmoid_table[static_cast<size_t>((s - a.min_sigmoid_input) * a.idx_factor)];
+}
+
+// pair (i < j in sorted order): computes p_lambda, p_hessian; returns false if the pair is skipped
+__device__ __forceinline__ bool LrPair(const LambdarankArgs& a, const double* s_score, const float* s_label, int i, int j,
+                                       double inverse_max_dcg, bool norm_on, double* p_lambda, double* p_hessian, bool* i_is_high) {
+  if (s_label[i] == s_label[j]) return false;
+  int high_rank, low_rank;
+  if (s_label[i] > s_label[j]) { high_rank = i; low_rank = j; } else { high_rank = j; low_rank = i; }
+  const double high_score = s_score[high_rank], low_score = s_score[low_rank];
+  const double high_label_gain = a.label_gain[static_cast<int>(s_label[high_rank])];
+  const double low_label_gain = a.label_gain[static_cast<int>(s_label[low_rank])];
+  const double high_discount = a.discount[high_rank], low_discount = a.discount[low_rank];
+  const double delta_score = high_score - low_score;
+  const double dcg_gap = high_label_gain - low_label_gain;
+  const double paired_discount = fabs(high_discount - low_discount);
+  double delta_pair_NDCG = dcg_gap * paired_discount * inverse_max_dcg;
+  if (norm_on) delta_pair_NDCG /= (0.01f + fabs(delta_score));
+  double pl = LrSigmoid(a, delta_score);
+  double ph = pl * (1.0f - pl);
+  pl *= -a.sigmoid * delta_pair_NDCG;
+  ph *= a.sigmoid * a.sigmoid * delta_pair_NDCG;
+  *p_lambda = pl; *p_hessian = ph; *i_is_high = (high_rank == i);
+  return true;
+}
+
+__global__ void k_grad_lambdarank(LambdarankArgs a) {
+  extern __shared__ __align__(16) unsigned char lr_smem[];
+  const int q = blockIdx.x;
+  const int start = a.qb[q];
+  const int cnt = a.qb[q + 1] - start;
+  double* s_score = reinterpret_cast<double*>(lr_smem);                 // [max_cnt] sorted by rank
+  float* s_label = reinterpret_cast<float*>(s_score + a.max_cnt);      // [max_cnt]
+  int* s_doc = reinterpret_cast<int*>(s_label + a.max_cnt);            // rank -> doc
+  __shared__ double s_norm;
+  const double* sc = a.score + start;
+  const float* lb = a.label + start;
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+    const double sd = sc[d];
+    int rank = 0;
+    for (int e = 0; e < cnt; ++e) {
+      const double se = sc[e];
+      rank += (se > sd) || (se == sd && e < d);
+    }
+    s_score[rank] = sd; s_label[rank] = lb[d]; s_doc[rank] = d;
+  }
+  __syncthreads();
+  const double inverse_max_dcg = a.inv_max_dcg[q];
+  const double best_score = s_score[0];
+  int worst_idx = cnt - 1;
+  if (worst_idx > 0 && s_score[worst_idx] == KMINSCORE) worst_idx -= 1;
+  const double worst_score = s_score[worst_idx];
+  const bool norm_on = a.norm && best_score != worst_score;
+  const int T = a.truncation_level;
+  const int imax = min(cnt - 1, T);      // i ranges over [0, imax)
+  for (int r = threadIdx.x; r < cnt; r += blockDim.x) {
+    float lam = 0.0f, hes = 0.0f;
+    if (s_score[r] != KMINSCORE) {
+      // as the later element j = r of pairs (i, r), i < min(r, imax)
+      for (int i = 0; i < min(r, imax); ++i) {
+        if (s_score[i] == KMINSCORE) continue;
+        double pl, ph; bool i_high;
+        if (!LrPair(a, s_score, s_label, i, r, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
+        if (i_high) lam -= static_cast<float>(pl); else lam += static_cast<float>(pl);   // r is low when i is high
+        hes += static_cast<float>(ph);
+      }
+      // as the earlier element i = r of pairs (r, j), j > r
+      if (r < imax) {
+        for (int j = r + 1; j < cnt; ++j) {
+          if (s_score[j] == KMINSCORE) continue;
+          double pl, ph; bool i_high;
+          if (!LrPair(a, s_score, s_label, r, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
+          if (i_high) lam += static_cast<float>(pl); else lam -= static_cast<float>(pl);
+          hes += static_cast<float>(ph);
+        }
+      }
+    }
+    a.grad[start + s_doc[r]] = lam;
+    a.hess[start + s_doc[r]] = hes;
+  }
+  if (a.norm) {
+    if (threadIdx.x == 0) {
+      double sum_lambdas = 0.0;
+      for (int i = 0; i < imax; ++i) {
+        if (s_score[i] == KMINSCORE) continue;
+        for (int j = i + 1; j < cnt; ++j) {
+          if (s_score[j] == KMINSCORE) continue;
+          double pl, ph; bool i_high;
+          if (!LrPair(a, s_score, s_label, i, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
+          sum_lambdas -= 2 * pl;
+        }
+      }
+      s_norm = (sum_lambdas > 0) ? SoftLog2(1 + sum_lambdas) / sum_lambdas : -1.0;
+    }
+    __syncthreads();
+    if (s_norm >= 0.0) {
+      const double nf = s_norm;
+      for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+        a.grad[start + d] = static_cast<float>(a.grad[start + d] * nf);
+        a.hess[start + d] = static_cast<float>(a.hess[start + d] * nf);
+      }
+    }
+  }
+  if (a.weight != nullptr) {
+    __syncthreads();
+    for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+      a.grad[start + d] = static_cast<float>(a.grad[start + d] * a.weight[start + d]);
+      a.hess[start + d] = static_cast<float>(a.hess[start + d] * a.weight[start + d]);
+    }
+  }
+}
+
+__global__ void k_add_constant(double* score, int n, double v) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] += v;
+}
+
+// max|g|, max|h| over rows (non-negative float bit patterns order like unsigned ints)
+__global__ void k_absmax(const float* __restrict__ grad, const float* __restrict__ hess, int n, TreeCtrl* ctrl) {
+  float mg = 0.0f, mh = 0.0f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    mg = fmaxf(mg, fabsf(grad[i]));
+    mh = fmaxf(mh, fabsf(hess[i]));
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    mh = fmaxf(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(&ctrl->max_abs_g_bits, __float_as_uint(mg));
+    atomicMax(&ctrl->max_abs_h_bits, __float_as_uint(mh));
+  }
+}
+
+__global__ void k_scales(TreeCtrl* ctrl, LearnerParams lp) {
+  const double max_g = __uint_as_float(ctrl->max_abs_g_bits);
+  const double max_h = __uint_as_float(ctrl->max_abs_h_bits);
+  if (lp.quantized) {
+    ctrl->grad_scale = max_g / static_cast<double>(lp.num_grad_quant_bins / 2);
+    ctrl->hess_scale = lp.const_hessian ? max_h : max_h / static_cast<double>(lp.num_grad_quant_bins);
+    ctrl->inv_grad_scale = 1.0f / ctrl->grad_scale;
+    ctrl->inv_hess_scale = 1.0f / ctrl->hess_scale;
+  } else {
+    // power-of-two fixed-point scales: |x| < 2^e  =>  |x * 2^(kFixBits - e)| < 2^kFixBits
+    int eg = 0, eh = 0;
+    if (max_g > 0.0) frexp(max_g, &eg);
+    if (max_h > 0.0) frexp(max_h, &eh);
+    ctrl->inv_grad_scale = ldexp(1.0, kFixBits - eg);
+    ctrl->inv_hess_scale = ldexp(1.0, kFixBits - eh);
+    ctrl->grad_scale = ldexp(1.0, eg - kFixBits);
+    ctrl->hess_scale = ldexp(1.0, eh - kFixBits);
+  }
+}
+
+__global__ void k_quantize(const float* __restrict__ grad, const float* __restrict__ hess, int n, const TreeCtrl* __restrict__ ctrl,
+                           LearnerParams lp, unsigned int iter, unsigned int row_offset, uint16_t* __restrict__ gh16,
+                           int2* __restrict__ ghfix) {
+  const double inv_g = ctrl->inv_grad_scale, inv_h = ctrl->inv_hess_scale;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float g = grad[i], h = hess[i];
+    if (lp.quantized) {
+      signed char qg, qh;
+      if (lp.stochastic_rounding) {
+        const float rg = HashUniform(lp.seed, iter, row_offset + i, 0);
+        const float rh = HashUniform(lp.seed, iter, row_offset + i, 1);
+        qg = g >= 0.0f ? static_cast<signed char>(g * inv_g + rg) : static_cast<signed char>(g * inv_g - rg);
+        qh = static_cast<signed char>(h * inv_h + rh);
+      } else {
+        qg = g >= 0.0f ? static_cast<signed char>(g * inv_g + 0.5f) : static_cast<signed char>(g * inv_g - 0.5f);
+        qh = static_cast<signed char>(h * inv_h + 0.5f);
+      }
+      gh16[i] = static_cast<uint16_t>((static_cast<unsigned int>(static_cast<unsigned char>(qg)) << 8) | static_cast<unsigned char>(qh));
+    } else {
+      ghfix[i] = make_int2(__double2int_rn(g * inv_g), __double2int_rn(h * inv_h));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K4 histogram
+// Shared-memory layout [array][bin][32 lanes]: in any one warp-wide atomic every lane hits its own bank, whatever the
+// bins are, so throughput does not depend on the bin distribution (measured on B200: 2.0-4.2 T updates/s against
+// 0.7-3.5 T/s for a [feature][bin] layout; profiles/r01_smem_atomics_microbench.log).  A lane covers BPL consecutive
+// feature bytes of one row; 32/R lanes cover one row record slice and R rows are handled per warp step, so each
+// feature has R private sub-histograms that are summed when the CTA flushes to the global int64 histogram.
+//   quantized: one ATOMS.ADD.U32 per (row, feature) on a packed (grad << 16) + hess word; a CTA flushes before any
+//              16-bit lane can overflow.
+//   float    : two ATOMS.ADD.U32 per (row, feature) on 32-bit fixed-point sums.
+// Algorithmic bytes per row visit: F * 1 (bins) + 2 (quantized g,h) or 8 (float) + 4 (row index; 0 at the root).
+template <int R, int BPL, bool FLT>
+__global__ void __launch_bounds__(kHistThreads, 1)
+k_hist(const uint8_t* __restrict__ rm, int rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+       const int* __restrict__ idx0, const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
+       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int root, int rows_per_flush) {
+  extern __shared__ unsigned int hsm[];
+  constexpr int LPR = 32 / R;                 // lanes per row
+  constexpr int FT = LPR * BPL;               // features per tile
+  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays
+  if (ctrl->done) return;
+  if (!root && !ctrl->find) return;
+  const LeafDev& lf = leaves[root ? 0 : ctrl->smaller];
+  const int begin = lf.begin, count = lf.count, buf = lf.buf;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0)
+    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
+  int rows_per_cta = (count + gridDim.x - 1) / gridDim.x;
+  rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
+  const int lo = blockIdx.x * rows_per_cta;
+  const int hi = min(count, lo + rows_per_cta);
+  if (lo >= hi) return;
+  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int q = lane % LPR, r = lane / LPR;
+  const int tile = blockIdx.y;
+  const size_t col_off = static_cast<size_t>(tile) * FT + q * BPL;
+  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
+  __syncthreads();
+  unsigned int* my = hsm + lane;
+  for (int sub = lo; sub < hi; sub += rows_per_flush) {
+    const int sub_hi = min(hi, sub + rows_per_flush);
+    for (int p0 = sub + warp * 32; p0 < sub_hi; p0 += nwarps * 32) {
+      const int p = p0 + lane;
+      const bool v = p < sub_hi;
+      int row_l = -1;
+      if (v) row_l = idx ? idx[begin + p] : begin + p;
+      unsigned int pk_l = 0; int gx_l = 0, hx_l = 0;
+      if (v) {
+        if (FLT) { const int2 t = ghfix[row_l]; gx_l = t.x; hx_l = t.y; }
+        else {
+          const unsigned int w = gh16[row_l];
+          pk_l = (static_cast<unsigned int>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+        }
+      }
+      constexpr int STEPS = 32 / R;
+      constexpr int U = STEPS < 8 ? STEPS : 8;
+      #pragma unroll 1
+      for (int s0 = 0; s0 < STEPS; s0 += U) {
+        int rows[U]; unsigned int bins[U];
+        #pragma unroll
+        for (int u = 0; u < U; ++u) {
+          rows[u] = __shfl_sync(0xffffffffu, row_l, (s0 + u) * R + r);
+          bins[u] = 0;
+          if (rows[u] >= 0) {
+            const uint8_t* src = rm + static_cast<size_t>(rows[u]) * rm_stride + col_off;
+            if (BPL == 4) bins[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
+            else bins[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
+          }
+        }
+        #pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int srcl = (s0 + u) * R + r;
+          if (FLT) {
+            const int gx = __shfl_sync(0xffffffffu, gx_l, srcl);
+            const int hx = __shfl_sync(0xffffffffu, hx_l, srcl);
+            if (rows[u] >= 0) {
+              #pragma unroll
+              for (int k = 0; k < BPL; ++k) {
+                const unsigned int bin = (bins[u] >> (8 * k)) & 0xffu;
+                atomicAdd(my + (2 * k) * (kBins * 32) + bin * 32, static_cast<unsigned int>(gx));
+                atomicAdd(my + (2 * k + 1) * (kBins * 32) + bin * 32, static_cast<unsigned int>(hx));
+              }
+            }
+          } else {
+            const unsigned int pk = __shfl_sync(0xffffffffu, pk_l, srcl);
+            if (rows[u] >= 0) {
+              #pragma unroll
+              for (int k = 0; k < BPL; ++k) {
+                const unsigned int bin = (bins[u] >> (8 * k)) & 0xffu;
+                atomicAdd(my + k * (kBins * 32) + bin * 32, pk);
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // flush: sum the R sub-histograms of each (feature, bin) and add into the global int64 histogram
+    for (int i = threadIdx.x; i < BPL * kBins * LPR; i += blockDim.x) {
+      const int qq = i % LPR;
+      const int bin = (i / LPR) % kBins;
+      const int k = i / (LPR * kBins);
+      const int f = tile * FT + qq * BPL + k;
+      long long g = 0, h = 0;
+      #pragma unroll
+      for (int rr = 0; rr < R; ++rr) {
+        const int a = bin * 32 + rr * LPR + qq;
+        if (FLT) {
+          g += static_cast<int>(hsm[(2 * k) * (kBins * 32) + a]);
+          h += static_cast<int>(hsm[(2 * k + 1) * (kBins * 32) + a]);
+          hsm[(2 * k) * (kBins * 32) + a] = 0u;
+          hsm[(2 * k + 1) * (kBins * 32) + a] = 0u;
+        } else {
+          const int w = static_cast<int>(hsm[k * (kBins * 32) + a]);
+          h += w & 0xffff;
+          g += w >> 16;
+          hsm[k * (kBins * 32) + a] = 0u;
+        }
+      }
+      if (f < F && (g != 0 || h != 0)) {
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
+        if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
+        if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K5 + K6 split search
+struct GainParams { double l1, l2, max_delta_step; };
+
+__device__ __forceinline__ double ThresholdL1D(double s, double l1) {
+  double reg = fabs(s) - l1;
+  if (reg < 0.0) reg = 0.0;
+  return SignD(s) * reg;
+}
+__device__ __forceinline__ double LeafOutputD(double g, double h, const LearnerParams& p) {
+  double ret = (p.l1 > 0.0) ? -ThresholdL1D(g, p.l1) / (h + p.l2) : -g / (h + p.l2);
+  if (p.max_delta_step > 0.0 && fabs(ret) > p.max_delta_step) ret = SignD(ret) * p.max_delta_step;
+  return ret;
+}
+__device__ __forceinline__ double LeafGainD(double g, double h, const LearnerParams& p) {
+  if (p.max_delta_step <= 0.0) {
+    const double sg = (p.l1 > 0.0) ? ThresholdL1D(g, p.l1) : g;
+    return (sg * sg) / (h + p.l2);
+  }
+  const double out = LeafOutputD(g, h, p);
+  const double sg = (p.l1 > 0.0) ? ThresholdL1D(g, p.l1) : g;
+  return -(2.0 * sg * out + (h + p.l2) * out * out);
+}
+__device__ __forceinline__ double SplitGainD(double lg, double lh, double rg, double rh, const LearnerParams& p) {
+  return LeafGainD(lg, lh, p) + LeafGainD(rg, rh, p);
+}
+
+struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right for reverse, left for forward)
+
+__device__ __forceinline__ Cand WarpBestCand(Cand c, bool prefer_larger_b) {
+  for (int o = 16; o > 0; o >>= 1) {
+    Cand t;
+    t.gain = __shfl_xor_sync(0xffffffffu, c.gain, o);
+    t.b = __shfl_xor_sync(0xffffffffu, c.b, o);
+    t.sg = __shfl_xor_sync(0xffffffffu, c.sg, o);
+    t.sh = __shfl_xor_sync(0xffffffffu, c.sh, o);
+    t.cnt = __shfl_xor_sync(0xffffffffu, c.cnt, o);
+    const bool better = (t.gain > c.gain) || (t.gain == c.gain && t.b >= 0 && (c.b < 0 || (prefer_larger_b ? t.b > c.b : t.b < c.b)));
+    if (better) c = t;
+  }
+  return c;
+}
+
+// One warp searches one feature of one leaf.  gz/hz: this lane's 8 bins (bins lane*8 .. lane*8+7), already the leaf's
+// histogram.  Implements FindBestThresholdSequentially / ...Int (reverse scan, plus forward scan when the feature has a
+// NaN bin and more than two bins) as prefix sums: the sequential `continue`/`break` conditions are monotone in the scan
+// position, so they reduce to per-threshold predicates.
+template <bool QUANT>
+__device__ void WarpFindBest(const long long (&gz_in)[8], const long long (&hz_in)[8], const FeatureMetaDev fm, int f,
+                             long long tot_g, long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data,
+                             const LearnerParams& P, double gscale, double hscale, SplitDev* out, unsigned char* splittable_out) {
+  const int lane = threadIdx.x & 31;
+  const int num_bin = fm.num_bin;
+  const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
+  const int nan_bin = two_scans ? num_bin - 1 : -1;
+  long long gz[8], hz[8];
+  int cz[8];
+  double sum_gradient, sum_hessian, cnt_factor;
+  if (QUANT) {
+    sum_gradient = static_cast<double>(tot_g) * gscale;
+    sum_hessian = static_cast<double>(tot_h) * hscale;
+    cnt_factor = static_cast<double>(num_data) / static_cast<double>(tot_h);
+  } else {
+    sum_gradient = leaf_sum_g;
+    sum_hessian = leaf_sum_h + 2 * KEPS;
+    cnt_factor = num_data / sum_hessian;
+  }
+  // inclusive prefix sums over bins, NaN bin (when scanned separately) and bins >= num_bin zeroed
+  long long pg = 0, ph = 0; int pc = 0;
+  #pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int b = lane * 8 + j;
+    const bool use = b < num_bin && b != nan_bin;
+    gz[j] = use ? gz_in[j] : 0; hz[j] = use ? hz_in[j] : 0;
+    cz[j] = (!QUANT && use) ? RoundIntD(static_cast<double>(hz[j]) * hscale * cnt_factor) : 0;
+    pg += gz[j]; ph += hz[j]; pc += cz[j];
+    gz[j] = pg; hz[j] = ph; cz[j] = pc;     // in-lane inclusive prefix
+  }
+  long long bg = pg, bh = ph; int bc = pc;  // warp exclusive prefix of lane totals
+  #pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long tg = __shfl_up_sync(0xffffffffu, bg, o);
+    const long long th = __shfl_up_sync(0xffffffffu, bh, o);
+    const int tc = __shfl_up_sync(0xffffffffu, bc, o);
+    if (lane >= o) { bg += tg; bh += th; bc += tc; }
+  }
+  const long long Tg = __shfl_sync(0xffffffffu, bg, 31), Th = __shfl_sync(0xffffffffu, bh, 31);
+  const int Tc = __shfl_sync(0xffffffffu, bc, 31);
+  bg -= pg; bh -= ph; bc -= pc;
+  const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
+  const double min_gain_shift = gain_shift + P.min_gain_to_split;
+  bool splittable = false;
+  // ---- reverse scan: right = bins [b, top], threshold = b - 1, b in [1, top]
+  const int top = num_bin - 1 - (two_scans ? 1 : 0);
+  Cand best_r; best_r.gain = KMINSCORE; best_r.b = -1; best_r.sg = 0; best_r.sh = 0; best_r.cnt = 0;
+  #pragma unroll
+  for (int j = 7; j >= 0; --j) {
+    const int b = lane * 8 + j;
+    if (b < 1 || b > top) continue;
+    // suffix sum from b = total - inclusive prefix(b - 1)
+    const long long incl_g_prev = bg + (j > 0 ? gz[j - 1] : 0), incl_h_prev = bh + (j > 0 ? hz[j - 1] : 0);
+    const long long rgi = Tg - incl_g_prev, rhi = Th - incl_h_prev;
+    double gain; int rc;
+    if (QUANT) {
+      rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+      const double srh = static_cast<double>(rhi) * hscale;
+      if (rc < P.min_data_in_leaf || srh < P.min_sum_hessian) continue;
+      const int lc = num_data - rc;
+      if (lc < P.min_data_in_leaf) continue;
+      const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
+      const double slh = static_cast<double>(lhi) * hscale;
+      if (slh < P.min_sum_hessian) continue;
+      gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+    } else {
+      rc = Tc - (bc + (j > 0 ? cz[j - 1] : 0));
+      const double rh = KEPS + static_cast<double>(rhi) * hscale;
+      if (rc < P.min_data_in_leaf || rh < P.min_sum_hessian) continue;
+      const int lc = num_data - rc;
+      if (lc < P.min_data_in_leaf) continue;
+      const double lh = sum_hessian - rh;
+      if (lh < P.min_sum_hessian) continue;
+      const double rg = static_cast<double>(rgi) * gscale;
+      gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P);
+    }
+    if (gain <= min_gain_shift) continue;
+    splittable = true;
+    if (gain > best_r.gain) { best_r.gain = gain; best_r.b = b; best_r.sg = rgi; best_r.sh = rhi; best_r.cnt = rc; }
+  }
+  best_r = WarpBestCand(best_r, true);
+  // ---- forward scan (NaN as missing): left = bins [0, b], threshold = b, b in [0, num_bin - 2]
+  Cand best_f; best_f.gain = KMINSCORE; best_f.b = -1; best_f.sg = 0; best_f.sh = 0; best_f.cnt = 0;
+  if (two_scans) {
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int b = lane * 8 + j;
+      if (b > num_bin - 2) continue;
+      const long long lgi = bg + gz[j], lhi = bh + hz[j];
+      double gain; int lc;
+      if (QUANT) {
+        lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        const double slh = static_cast<double>(lhi) * hscale;
+        if (lc < P.min_data_in_leaf || slh < P.min_sum_hessian) continue;
+        const int rc = num_data - lc;
+        if (rc < P.min_data_in_leaf) continue;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double srh = static_cast<double>(rhi) * hscale;
+        if (srh < P.min_sum_hessian) continue;
+        gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      } else {
+        lc = bc + cz[j];
+        const double lh = KEPS + static_cast<double>(lhi) * hscale;
+        if (lc < P.min_data_in_leaf || lh < P.min_sum_hessian) continue;
+        const int rc = num_data - lc;
+        if (rc < P.min_data_in_leaf) continue;
+        const double rh = sum_hessian - lh;
+        if (rh < P.min_sum_hessian) continue;
+        const double lg = static_cast<double>(lgi) * gscale;
+        gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P);
+      }
+      if (gain <= min_gain_shift) continue;
+      splittable = true;
+      if (gain > best_f.gain) { best_f.gain = gain; best_f.b = b; best_f.sg = lgi; best_f.sh = lhi; best_f.cnt = lc; }
+    }
+    best_f = WarpBestCand(best_f, false);
+  }
+  splittable = __any_sync(0xffffffffu, splittable);
+  if (lane == 0) {
+    SplitDev s;
+    s.gain = KMINSCORE; s.feature = f; s.real_feature = fm.real_index; s.threshold = 0; s.default_left = 1;
+    s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
+    s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
+    s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      const Cand& c = pass == 0 ? best_r : best_f;
+      if (pass == 1 && !two_scans) break;
+      if (!(splittable && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      const bool reverse = pass == 0;
+      if (QUANT) {
+        const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double blg = static_cast<double>(lgi) * gscale, blh = static_cast<double>(lhi) * hscale;
+        const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
+        s.threshold = reverse ? c.b - 1 : c.b;
+        s.left_output = LeafOutputD(blg, blh, P);
+        s.left_count = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = lgi; s.left_int_h = lhi;
+        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_count = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+        s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
+      } else {
+        double best_lg, best_lh; int left_count;
+        if (reverse) {
+          const double rg = static_cast<double>(c.sg) * gscale, rh = KEPS + static_cast<double>(c.sh) * hscale;
+          best_lg = sum_gradient - rg; best_lh = sum_hessian - rh; left_count = num_data - c.cnt;
+        } else {
+          best_lg = static_cast<double>(c.sg) * gscale; best_lh = KEPS + static_cast<double>(c.sh) * hscale; left_count = c.cnt;
+        }
+        s.threshold = reverse ? c.b - 1 : c.b;
+        s.left_output = LeafOutputD(best_lg, best_lh, P);
+        s.left_count = left_count;
+        s.left_sum_g = best_lg; s.left_sum_h = best_lh - KEPS;
+        s.right_output = LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P);
+        s.right_count = num_data - left_count;
+        s.right_sum_g = sum_gradient - best_lg; s.right_sum_h = sum_hessian - best_lh - KEPS;
+      }
+      s.gain = c.gain - min_gain_shift;
+      s.default_left = reverse ? 1 : 0;
+    }
+    if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    *out = s;
+    *splittable_out = splittable ? 1 : 0;
+  }
+}
+
+// One warp per feature: stores the freshly built (smaller child's) histogram into its pool slot, derives the sibling
+// by subtraction from the parent's slot (K5), and searches both (K6).  root=1: only leaf 0, whose totals are the sum of
+// any feature's bins.
+template <bool QUANT>
+__global__ void __launch_bounds__(256) k_find(const long long* __restrict__ work, long long* __restrict__ pool,
+                                              const FeatureMetaDev* __restrict__ fmeta, LeafDev* __restrict__ leaves,
+                                              TreeCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
+                                              unsigned char* __restrict__ splittable, LearnerParams P, int root) {
+  if (ctrl->done) return;
+  if (!root && !ctrl->find) return;
+  const int F = P.num_features;
+  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (f >= F) return;
+  const int lane = threadIdx.x & 31;
+  const FeatureMetaDev fm = fmeta[f];
+  const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
+  const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
+  const long long* w = work + static_cast<size_t>(f) * kBins * 2 + lane * 16;
+  long long g[8], h[8];
+  #pragma unroll
+  for (int j = 0; j < 8; j += 1) {
+    const longlong2 v = *reinterpret_cast<const longlong2*>(w + 2 * j);
+    g[j] = v.x; h[j] = v.y;
+  }
+  if (root) {
+    long long tg = 0, th = 0;
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) { tg += g[j]; th += h[j]; }
+    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
+    long long* dst = pool + static_cast<size_t>(leaves[0].hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<longlong2*>(dst + 2 * j) = make_longlong2(g[j], h[j]);
+    const double sg = static_cast<double>(tg) * gscale, sh = static_cast<double>(th) * hscale;
+    if (f == 0 && lane == 0) { leaves[0].int_g = tg; leaves[0].int_h = th; leaves[0].sum_g = sg; leaves[0].sum_h = sh; }
+    WarpFindBest<QUANT>(g, h, fm, f, tg, th, sg, sh, leaves[0].global_count, P, gscale, hscale, feat_best + f, splittable + f);
+    return;
+  }
+  const int sm = ctrl->smaller, lg = ctrl->larger;
+  const int left = ctrl->cur_leaf;
+  const bool used = splittable[static_cast<size_t>(left) * F + f] != 0;     // the parent's flag (the left child reuses its id)
+  const LeafDev& Ls = leaves[sm];
+  const LeafDev& Ll = leaves[lg];
+  long long* ds = pool + static_cast<size_t>(Ls.hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
+  long long* dl = pool + static_cast<size_t>(Ll.hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
+  const long long* dp = pool + static_cast<size_t>(ctrl->parent_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
+  long long pgv[8], phv[8];
+  #pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const longlong2 v = *reinterpret_cast<const longlong2*>(dp + 2 * j);
+    pgv[j] = v.x - g[j]; phv[j] = v.y - h[j];
+  }
+  #pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    *reinterpret_cast<longlong2*>(ds + 2 * j) = make_longlong2(g[j], h[j]);
+    *reinterpret_cast<longlong2*>(dl + 2 * j) = make_longlong2(pgv[j], phv[j]);
+  }
+  SplitDev* outs = feat_best + f;
+  SplitDev* outl = feat_best + F + f;
+  unsigned char* spl_s = splittable + static_cast<size_t>(sm) * F + f;
+  unsigned char* spl_l = splittable + static_cast<size_t>(lg) * F + f;
+  if (!used) {
+    if (lane == 0) {
+      SplitDev s;
+      s.gain = KMINSCORE; s.feature = f; s.real_feature = fm.real_index; s.threshold = 0; s.default_left = 1;
+      s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
+      s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
+      s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
+      *outs = s; *outl = s; *spl_s = 0; *spl_l = 0;
+    }
+    return;
+  }
+  WarpFindBest<QUANT>(g, h, fm, f, Ls.int_g, Ls.int_h, Ls.sum_g, Ls.sum_h, Ls.global_count, P, gscale, hscale, outs, spl_s);
+  WarpFindBest<QUANT>(pgv, phv, fm, f, Ll.int_g, Ll.int_h, Ll.sum_g, Ll.sum_h, Ll.global_count, P, gscale, hscale, outl, spl_l);
+}
+
+// ------------------------------------------------------------------------------------------------ leaf selection + Tree::Split
+__device__ __forceinline__ bool SplitBetter(double ga, int fa, double gb, int fb) {
+  // upstream SplitInfo::operator>: larger gain; equal gain -> smaller real feature index (-1 = +inf)
+  const int a = fa < 0 ? 0x7fffffff : fa, b = fb < 0 ? 0x7fffffff : fb;
+  if (ga != gb) return ga > gb;
+  return a < b;
+}
+
+__global__ void __launch_bounds__(256) k_select(LeafDev* __restrict__ leaves, TreeCtrl* __restrict__ ctrl,
+                                                const SplitDev* __restrict__ feat_best, TreeArraysDev T,
+                                                const FeatureMetaDev* __restrict__ fmeta, LearnerParams P) {
+  if (ctrl->done) return;
+  __shared__ double s_gain[256];
+  __shared__ int s_feat[256], s_idx[256];
+  const int F = P.num_features;
+  // (1) reduce the per-feature results of the leaves searched by the previous k_find
+  const int pending = ctrl->pending;
+  for (int c = 0; c < pending; ++c) {
+    const SplitDev* fb = feat_best + static_cast<size_t>(c) * F;
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int f = threadIdx.x; f < F; f += blockDim.x) {
+      const double g = fb[f].gain; const int rf = fb[f].real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = f; }
+    }
+    s_gain[threadIdx.x] = bg; s_feat[threadIdx.x] = bf; s_idx[threadIdx.x] = bi;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        const int t = threadIdx.x + o;
+        if (s_idx[t] >= 0 && (s_idx[threadIdx.x] < 0 || SplitBetter(s_gain[t], s_feat[t], s_gain[threadIdx.x], s_feat[threadIdx.x]))) {
+          s_gain[threadIdx.x] = s_gain[t]; s_feat[threadIdx.x] = s_feat[t]; s_idx[threadIdx.x] = s_idx[t];
+        }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      const int leaf = (pending == 1) ? 0 : (c == 0 ? ctrl->smaller : ctrl->larger);
+      leaves[leaf].best = fb[s_idx[0]];
+    }
+    __syncthreads();
+  }
+  // (2) leaf with the best split: (gain desc, feature asc, leaf asc)
+  const int nl = ctrl->num_leaves;
+  {
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int l = threadIdx.x; l < nl; l += blockDim.x) {
+      const double g = leaves[l].best.gain; const int rf = leaves[l].best.real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = l; }
+    }
+    s_gain[threadIdx.x] = bg; s_feat[threadIdx.x] = bf; s_idx[threadIdx.x] = bi;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        const int t = threadIdx.x + o;
+        if (s_idx[t] >= 0) {
+          const bool better = s_idx[threadIdx.x] < 0 || SplitBetter(s_gain[t], s_feat[t], s_gain[threadIdx.x], s_feat[threadIdx.x]) ||
+                              (!SplitBetter(s_gain[threadIdx.x], s_feat[threadIdx.x], s_gain[t], s_feat[t]) && s_idx[t] < s_idx[threadIdx.x]);
+          if (better) { s_gain[threadIdx.x] = s_gain[t]; s_feat[threadIdx.x] = s_feat[t]; s_idx[threadIdx.x] = s_idx[t]; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x != 0) return;
+  ctrl->pending = 0;
+  const int best_leaf = s_idx[0];
+  const SplitDev bs = leaves[best_leaf].best;
+  if (!(bs.gain > 0.0) || nl >= P.num_leaves) { ctrl->done = 1; return; }
+  // (3) Tree::Split bookkeeping
+  const int new_node = nl - 1, new_leaf = nl;
+  const FeatureMetaDev fm = fmeta[bs.feature];
+  const int parent = T.leaf_parent[best_leaf];
+  if (parent >= 0) {
+    if (T.left_child[parent] == ~best_leaf) T.left_child[parent] = new_node; else T.right_child[parent] = new_node;
+  }
+  T.split_feature_inner[new_node] = bs.feature;
+  T.split_gain[new_node] = static_cast<float>(bs.gain);
+  T.left_child[new_node] = ~best_leaf;
+  T.right_child[new_node] = ~new_leaf;
+  T.leaf_parent[best_leaf] = new_node;
+  T.leaf_parent[new_leaf] = new_node;
+  T.internal_weight[new_node] = bs.left_sum_h + bs.right_sum_h;
+  T.internal_value[new_node] = T.leaf_value[best_leaf];
+  T.internal_count[new_node] = bs.left_count + bs.right_count;
+  T.leaf_value[best_leaf] = (bs.left_output != bs.left_output) ? 0.0 : bs.left_output;
+  T.leaf_weight[best_leaf] = bs.left_sum_h;
+  T.leaf_count[best_leaf] = bs.left_count;
+  T.leaf_value[new_leaf] = (bs.right_output != bs.right_output) ? 0.0 : bs.right_output;
+  T.leaf_weight[new_leaf] = bs.right_sum_h;
+  T.leaf_count[new_leaf] = bs.right_count;
+  T.leaf_depth[new_leaf] = T.leaf_depth[best_leaf] + 1;
+  T.leaf_depth[best_leaf]++;
+  signed char dt = 0;
+  if (bs.default_left) dt |= 2;
+  dt |= static_cast<signed char>((fm.missing_type & 3) << 2);
+  T.decision_type[new_node] = dt;
+  T.threshold_in_bin[new_node] = bs.threshold;
+  ctrl->num_leaves = nl + 1;
+  ctrl->cur_leaf = best_leaf; ctrl->new_leaf = new_leaf; ctrl->cur_node = new_node;
+  ctrl->cur_feature = bs.feature; ctrl->cur_threshold = bs.threshold; ctrl->cur_default_left = bs.default_left;
+  ctrl->cur_nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
+  ctrl->src_begin = leaves[best_leaf].begin; ctrl->src_count = leaves[best_leaf].count; ctrl->src_buf = leaves[best_leaf].buf;
+  ctrl->parent_slot = leaves[best_leaf].hist_slot;
+}
+
+// ------------------------------------------------------------------------------------------------ K7 stable partition
+// pass 1: left/right flag of every row of the leaf as one ballot word per warp + per-block left counts
+__global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __restrict__ cm, long long n_pad,
+                                                             const int* __restrict__ idx0, const int* __restrict__ idx1,
+                                                             const TreeCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
+                                                             int* __restrict__ block_counts) {
+  if (ctrl->done) return;
+  const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
+  const int thr = ctrl->cur_threshold, nan_bin = ctrl->cur_nan_bin, dl = ctrl->cur_default_left;
+  const uint8_t* col = cm + static_cast<size_t>(ctrl->cur_feature) * n_pad;
+  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
+  int chunk = (n + gridDim.x - 1) / gridDim.x;
+  chunk = (chunk + kPartThreads - 1) / kPartThreads * kPartThreads;
+  const int lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
+  int cnt = 0;
+  for (int tile = lo; tile < hi; tile += kPartThreads) {
+    const int p = tile + threadIdx.x;
+    bool left = false;
+    if (p < hi) {
+      const int row = idx ? idx[begin + p] : begin + p;
+      const int bin = col[row];
+      left = (bin == nan_bin) ? (dl != 0) : (bin <= thr);
+    }
+    const unsigned int word = __ballot_sync(0xffffffffu, left);
+    if ((threadIdx.x & 31) == 0 && p < hi) flags[p >> 5] = word;
+    cnt += left;
+  }
+  __shared__ int s_cnt[kPartThreads / 32];
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int i = 0; i < kPartThreads / 32; ++i) t += s_cnt[i];
+    block_counts[blockIdx.x] = t;
+  }
+}
+
+// pass 2: scatter into the other index buffer keeping order; block 0 also publishes the two children
+__global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __restrict__ idx0r, const int* __restrict__ idx1r,
+                                                               int* __restrict__ idx0w, int* __restrict__ idx1w,
+                                                               TreeCtrl* __restrict__ ctrl, LeafDev* __restrict__ leaves,
+                                                               const unsigned int* __restrict__ flags,
+                                                               const int* __restrict__ block_counts, TreeArraysDev T,
+                                                               unsigned char* __restrict__ splittable, LearnerParams P) {
+  if (ctrl->done) return;
+  const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
+  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
+  const int other = buf < 0 ? 0 : 1 - buf;
+  int* dst = other == 0 ? idx0w : idx1w;
+  __shared__ int s_red[2][kPartThreads / 32];
+  __shared__ int s_wcnt[kPartThreads / 32];
+  int before = 0, total = 0;
+  for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+    const int c = block_counts[i];
+    total += c;
+    if (i < blockIdx.x) before += c;
+  }
+  for (int o = 16; o > 0; o >>= 1) { before += __shfl_xor_sync(0xffffffffu, before, o); total += __shfl_xor_sync(0xffffffffu, total, o); }
+  if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = before; s_red[1][threadIdx.x >> 5] = total; }
+  __syncthreads();
+  before = 0; total = 0;
+  for (int i = 0; i < kPartThreads / 32; ++i) { before += s_red[0][i]; total += s_red[1][i]; }
+  int chunk = (n + gridDim.x - 1) / gridDim.x;
+  chunk = (chunk + kPartThreads - 1) / kPartThreads * kPartThreads;
+  const int lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int running = before;
+  for (int tile = lo; tile < hi; tile += kPartThreads) {
+    const int p = tile + threadIdx.x;
+    const int wbase = tile + warp * 32;
+    const unsigned int word = (wbase < hi) ? flags[wbase >> 5] : 0u;
+    if (lane == 0) s_wcnt[warp] = __popc(word);
+    __syncthreads();
+    int wprefix = 0, tile_total = 0;
+    for (int i = 0; i < kPartThreads / 32; ++i) { const int c = s_wcnt[i]; tile_total += c; if (i < warp) wprefix += c; }
+    if (p < hi) {
+      const int row = idx ? idx[begin + p] : begin + p;
+      const int lefts_before = running + wprefix + __popc(word & ((1u << lane) - 1u));
+      if ((word >> lane) & 1u) dst[begin + lefts_before] = row;
+      else dst[begin + total + (p - lefts_before)] = row;
+    }
+    running += tile_total;
+    __syncthreads();
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int left = ctrl->cur_leaf, right = ctrl->new_leaf, node = ctrl->cur_node;
+    const SplitDev bs = leaves[left].best;
+    const int nl_true = total, nr_true = n - total;
+    int lc = bs.left_count, rc = bs.right_count;
+    if (!P.dp) {   // serial learner: SplitInfo counts are replaced by the true partition counts
+      lc = nl_true; rc = nr_true;
+      T.leaf_count[left] = lc; T.leaf_count[right] = rc; T.internal_count[node] = lc + rc;
+    }
+    LeafDev L = leaves[left], Rr = leaves[right];
+    const int fresh_slot = Rr.hist_slot, parent_slot = L.hist_slot, depth = L.depth + 1;
+    L.begin = begin; L.count = nl_true; L.buf = other; L.global_count = lc;
+    L.int_g = bs.left_int_g; L.int_h = bs.left_int_h; L.sum_g = bs.left_sum_g; L.sum_h = bs.left_sum_h; L.depth = depth;
+    Rr.begin = begin + nl_true; Rr.count = nr_true; Rr.buf = other; Rr.global_count = rc;
+    Rr.int_g = bs.right_int_g; Rr.int_h = bs.right_int_h; Rr.sum_g = bs.right_sum_g; Rr.sum_h = bs.right_sum_h; Rr.depth = depth;
+    L.best.gain = KMINSCORE; L.best.feature = -1; L.best.real_feature = -1;
+    Rr.best.gain = KMINSCORE; Rr.best.feature = -1; Rr.best.real_feature = -1;
+    const bool left_smaller = lc < rc;
+    const int smaller = left_smaller ? left : right, larger = left_smaller ? right : left;
+    if (left_smaller) { L.hist_slot = fresh_slot; Rr.hist_slot = parent_slot; }
+    // BeforeFindBestSplit
+    bool find = true;
+    if (P.max_depth > 0 && depth >= P.max_depth) find = false;
+    if (rc < P.min_data_in_leaf * 2 && lc < P.min_data_in_leaf * 2) find = false;
+    leaves[left] = L; leaves[right] = Rr;
+    ctrl->smaller = smaller; ctrl->larger = larger; ctrl->find = find ? 1 : 0; ctrl->pending = find ? 2 : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K8 score update
+// Leaf ranges partition [0, n); ranges are looked up by position.  score[row] += shrunk leaf value.
+__global__ void __launch_bounds__(256) k_sort_leaves(const LeafDev* __restrict__ leaves, const TreeCtrl* __restrict__ ctrl,
+                                                     int* __restrict__ sorted /*[2*L]: leaf ids then begins*/, int L) {
+  const int nl = ctrl->num_leaves;
+  for (int i = threadIdx.x; i < nl; i += blockDim.x) {
+    const int bi = leaves[i].begin, ci = leaves[i].count;
+    int rank = 0;
+    for (int j = 0; j < nl; ++j) {
+      const int bj = leaves[j].begin, cj = leaves[j].count;
+      // order by begin; an empty range sorts before the non-empty range that starts at the same position
+      rank += (bj < bi) || (bj == bi && (cj < ci || (cj == ci && j < i)));
+    }
+    sorted[rank] = i;
+    sorted[L + rank] = bi;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_score_update(double* __restrict__ score, const int* __restrict__ idx0,
+                                                      const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
+                                                      const TreeCtrl* __restrict__ ctrl, const int* __restrict__ sorted, int L,
+                                                      const double* __restrict__ leaf_value, double lr, int n) {
+  __shared__ int s_begin[1024], s_leaf[1024];
+  __shared__ double s_val[1024];
+  __shared__ int s_buf[1024];
+  const int nl = ctrl->num_leaves;
+  if (nl <= 1) return;
+  for (int i = threadIdx.x; i < nl; i += blockDim.x) {
+    const int leaf = sorted[i];
+    s_leaf[i] = leaf; s_begin[i] = sorted[L + i]; s_buf[i] = leaves[leaf].buf;
+    double v = leaf_value[leaf] * lr;
+    const double zt = (double)1e-35f;
+    if (v >= -zt && v <= zt) v = 0.0;
+    s_val[i] = v;
+  }
+  __syncthreads();
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    int lo = 0, hi = nl - 1;      // last i with s_begin[i] <= p
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_begin[mid] <= p) lo = mid; else hi = mid - 1;
+    }
+    const int row = (s_buf[lo] == 0 ? idx0 : idx1)[p];
+    score[row] += s_val[lo];
+  }
+}
+
+__global__ void k_tree_init(LeafDev* leaves, TreeCtrl* ctrl, TreeArraysDev T, int L, int n_local, int n_global) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < L) {
+    LeafDev z;
+    z.begin = 0; z.count = 0; z.buf = -1; z.global_count = 0; z.int_g = z.int_h = 0; z.sum_g = z.sum_h = 0.0;
+    z.depth = 0; z.hist_slot = i;
+    z.best.gain = KMINSCORE; z.best.feature = -1; z.best.real_feature = -1; z.best.threshold = 0; z.best.default_left = 1;
+    z.best.left_count = z.best.right_count = 0; z.best.left_output = z.best.right_output = 0.0;
+    z.best.left_sum_g = z.best.left_sum_h = z.best.right_sum_g = z.best.right_sum_h = 0.0;
+    z.best.left_int_g = z.best.left_int_h = z.best.right_int_g = z.best.right_int_h = 0;
+    if (i == 0) { z.count = n_local; z.global_count = n_global; }
+    leaves[i] = z;
+    T.leaf_parent[i] = -1; T.leaf_depth[i] = 0; T.leaf_value[i] = 0.0; T.leaf_weight[i] = 0.0; T.leaf_count[i] = 0;
+    if (i < L - 1) {
+      T.left_child[i] = 0; T.right_child[i] = 0; T.split_feature_inner[i] = 0; T.threshold_in_bin[i] = 0;
+      T.internal_count[i] = 0; T.decision_type[i] = 0; T.split_gain[i] = 0.0f; T.internal_value[i] = 0.0; T.internal_weight[i] = 0.0;
+    }
+  }
+  if (i == 0) {
+    ctrl->num_leaves = 1; ctrl->done = 0; ctrl->pending = 1; ctrl->find = 1; ctrl->smaller = 0; ctrl->larger = -1;
+    ctrl->cur_leaf = 0; ctrl->new_leaf = 0;
+  }
+}
+
+}  // namespace lgb

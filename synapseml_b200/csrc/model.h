@@ -1,0 +1,39 @@
+// Host-side tree container and the LightGBM text model (format: SURVEY.md A.10).  The text model is the only output of
+// training the reference reads back: LGBM_BoosterSaveModelToStringSWIG at
+// lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:272-278
+// (called from BasePartitionTask.scala:450-461).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace lgb {
+
+struct HostTree {
+  int num_leaves = 1;
+  double shrinkage = 1.0;
+  std::vector<int> left_child, right_child, split_feature_inner, split_feature, leaf_count, internal_count, leaf_depth;
+  std::vector<int> threshold_in_bin;
+  std::vector<int8_t> decision_type;
+  std::vector<float> split_gain;
+  std::vector<double> threshold, leaf_value, leaf_weight, internal_value, internal_weight;
+
+  void Shrinkage(double rate);
+  void AddBias(double val);
+  void AsConstantTree(double val);
+  std::string ToString() const;
+  int GetLeaf(const double* row) const;
+  double Predict(const double* row) const { return leaf_value[GetLeaf(row)]; }
+};
+
+struct ModelHeader {
+  int max_feature_idx = 0;
+  std::string objective;
+  std::vector<std::string> feature_names;
+  std::vector<std::string> feature_infos;
+  std::vector<std::pair<std::string, std::string>> parameters;
+};
+
+std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration);
+
+}  // namespace lgb

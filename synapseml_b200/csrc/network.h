@@ -1,0 +1,51 @@
+// Collectives for the data-parallel learner.  The reference's LGBM_NetworkInit(machines, port, timeout, n)
+// (lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/NetworkManager.scala:195-218) builds a TCP mesh
+// inside lightgbmlib and LGBM_NetworkFree (BasePartitionTask.scala:282) tears it down.  Here the same two calls
+// bootstrap an NCCL communicator instead: the machine list the Scala NetworkManager already assembles is used once,
+// to hand rank 0's ncclUniqueId to the other ranks over TCP; histograms and split records then move over NVLink.
+// One process per GPU; rank = position of this process's "host:port" in the machine list.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <string>
+#include <vector>
+
+namespace lgb {
+
+class Network {
+ public:
+  static Network* Get();
+  void Init(const char* machines, int local_listen_port, int listen_time_out_s, int num_machines);
+  void Free();
+  int rank() const { return rank_; }
+  int world() const { return world_; }
+  bool active() const { return world_ > 1; }
+  void EnsureComm(int device);
+
+  // device-buffer collectives, enqueued on `stream`
+  void AllReduceSumInt64(long long* buf, size_t n, cudaStream_t stream);
+  void AllReduceMaxU32(unsigned int* buf, size_t n, cudaStream_t stream);
+  void ReduceScatterSumInt64(const long long* send, long long* recv, size_t recv_count, cudaStream_t stream);
+  void AllGatherBytes(const void* send, void* recv, size_t bytes_per_rank, cudaStream_t stream);
+  // small host-value collectives (blocking); used at set-up time only
+  void HostAllReduceSum(double* vals, int n);
+  void HostAllGatherInt64(long long mine, std::vector<long long>* all);
+
+  // parse "h:p,h:p,..." and find this process's rank; exposed for CPU tests
+  static std::vector<std::pair<std::string, int>> ParseMachines(const std::string& machines);
+  static int FindRank(const std::vector<std::pair<std::string, int>>& m, int local_listen_port);
+  // TCP hand-off of an opaque blob from rank 0 to everyone (the ncclUniqueId); exposed for CPU tests
+  static void BroadcastBlob(const std::vector<std::pair<std::string, int>>& m, int rank, int timeout_s, void* blob, size_t bytes);
+
+ private:
+  int rank_ = 0, world_ = 1, device_ = -1;
+  unsigned char unique_id_[128];
+  void* comm_ = nullptr;
+  void* nccl_lib_ = nullptr;
+  void* scratch_ = nullptr;    // small device scratch for the host-value collectives
+  cudaStream_t host_stream_ = nullptr;
+  void LoadNccl();
+};
+
+}  // namespace lgb
