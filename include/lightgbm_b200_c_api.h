@@ -132,7 +132,14 @@ int LGBM_B200_BoosterGetQuantGradients(BoosterHandle handle, int8_t* grad, int8_
 int LGBM_B200_BoosterRootHistogram(BoosterHandle handle, int64_t* out /* F_used*256*2 */);
 int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float* out_ms);
 int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable);
-int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches);
+int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches,
+                              int64_t* hist_launches);
+/* the TCP hand-off LGBM_NetworkInit uses for the NCCL unique id (CPU-only; for tests of the multi-process path) */
+int LGBM_B200_NetworkBootstrapBlob(const char* machines, int local_listen_port, int listen_time_out, uint8_t* blob, int32_t bytes,
+                                   int* out_rank);
+/* CUDA events on the booster's own stream (the stream every kernel of the training loop is launched on) */
+int LGBM_B200_BoosterTimerStart(BoosterHandle handle);
+int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms);
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
 
 #ifdef __cplusplus

@@ -107,6 +107,7 @@ Booster::~Booster() {
   cudaSetDevice(device_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
   for (auto& e : hist_events_) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+  if (timer_ev_[0]) { cudaEventDestroy(timer_ev_[0]); cudaEventDestroy(timer_ev_[1]); }
 }
 
 void Booster::Sync() const { LGB_CUDA(cudaStreamSynchronize(stream_)); }
@@ -322,7 +323,8 @@ void Booster::FetchTree(HostTree* t) {
   LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_.p, sizeof(TreeCtrl), cudaMemcpyDeviceToHost, stream_));
   Sync();
   last_rows_visited_ += hc.hist_rows;
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, sizeof(long long), stream_));
+  hist_launches_ += hc.hist_launches;
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, 2 * sizeof(long long), stream_));
   const int nl = hc.num_leaves;
   t->num_leaves = nl;
   t->shrinkage = 1.0;
@@ -500,6 +502,21 @@ void Booster::DebugRootHistogram(long long* out) {
   LaunchHist(true);
   Sync();
   LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, d_hist_work_.bytes(), cudaMemcpyDeviceToHost));
+}
+
+void Booster::TimerStart() {
+  LGB_CUDA(cudaSetDevice(device_));
+  if (!timer_ev_[0]) { LGB_CUDA(cudaEventCreate(&timer_ev_[0])); LGB_CUDA(cudaEventCreate(&timer_ev_[1])); }
+  LGB_CUDA(cudaEventRecord(timer_ev_[0], stream_));
+}
+
+float Booster::TimerStop() {
+  LGB_CHECK(timer_ev_[0] != nullptr, "TimerStop without TimerStart");
+  LGB_CUDA(cudaEventRecord(timer_ev_[1], stream_));
+  LGB_CUDA(cudaEventSynchronize(timer_ev_[1]));
+  float ms = 0;
+  LGB_CUDA(cudaEventElapsedTime(&ms, timer_ev_[0], timer_ev_[1]));
+  return ms;
 }
 
 float Booster::TimeRootHistogram(int repeats) {

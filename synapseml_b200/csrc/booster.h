@@ -47,6 +47,7 @@ struct TreeCtrl {
   double grad_scale, hess_scale;      // quantized: int -> float scales.  float mode: fixed-point -> float (powers of two)
   double inv_grad_scale, inv_hess_scale;
   long long hist_rows;              // rows visited by histogram launches since the host last cleared it
+  long long hist_launches;          // histogram launches that did work since the host last cleared it
 };
 
 struct TreeArraysDev {
@@ -85,9 +86,12 @@ class Booster {
   void DebugRootHistogram(long long* out);
   float TimeRootHistogram(int repeats);
   int64_t last_hist_rows_visited() const { return last_rows_visited_; }
+  int64_t hist_launches() const { return hist_launches_; }
   double last_hist_ms() const { return last_hist_ms_; }
   int launches() const { return launches_; }
   void EnableHistTiming(bool on) { time_hist_ = on; }
+  void TimerStart();
+  float TimerStop();      // ms between TimerStart and now, measured with CUDA events on the launching stream
 
  private:
   Dataset* ds_;
@@ -129,11 +133,12 @@ class Booster {
 
   // measurement
   bool time_hist_ = false;
-  int64_t last_rows_visited_ = 0;
+  int64_t last_rows_visited_ = 0, hist_launches_ = 0;
   double last_hist_ms_ = 0;
   int launches_ = 0;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;
+  cudaEvent_t timer_ev_[2] = {nullptr, nullptr};
 
   void InitObjective();
   double BoostFromScoreLocalSums(double* suml, double* sumw) const;

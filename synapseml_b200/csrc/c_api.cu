@@ -310,12 +310,26 @@ int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float*
   API_END();
 }
 int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable) { API_BEGIN(); static_cast<Booster*>(handle)->EnableHistTiming(enable != 0); API_END(); }
-int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches) {
+int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches,
+                              int64_t* hist_launches) {
   API_BEGIN();
   auto b = static_cast<Booster*>(handle);
-  *hist_rows_visited = b->last_hist_rows_visited(); *hist_ms = b->last_hist_ms(); *kernel_launches = b->launches();
+  *hist_rows_visited = b->last_hist_rows_visited(); *hist_ms = b->last_hist_ms(); *kernel_launches = b->launches(); *hist_launches = b->hist_launches();
   API_END();
 }
+// TCP hand-off used by LGBM_NetworkInit to distribute the NCCL unique id, exposed so the multi-process path can be tested
+// without GPUs: rank 0 (first entry of `machines`) sends `blob`, every other rank receives it in place.
+int LGBM_B200_NetworkBootstrapBlob(const char* machines, int local_listen_port, int listen_time_out, uint8_t* blob, int32_t bytes,
+                                   int* out_rank) {
+  API_BEGIN();
+  auto m = Network::ParseMachines(machines ? machines : "");
+  const int r = Network::FindRank(m, local_listen_port);
+  Network::BroadcastBlob(m, r, listen_time_out, blob, static_cast<size_t>(bytes));
+  *out_rank = r;
+  API_END();
+}
+int LGBM_B200_BoosterTimerStart(BoosterHandle handle) { API_BEGIN(); static_cast<Booster*>(handle)->TimerStart(); API_END(); }
+int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms) { API_BEGIN(); *out_ms = static_cast<Booster*>(handle)->TimerStop(); API_END(); }
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out) {
   API_BEGIN();
   static_cast<Booster*>(handle)->PredictRaw(data, nrow, ncol, out);

@@ -279,8 +279,10 @@ k_hist(const uint8_t* __restrict__ rm, int rm_stride, const uint16_t* __restrict
   if (!root && !ctrl->find) return;
   const LeafDev& lf = leaves[root ? 0 : ctrl->smaller];
   const int begin = lf.begin, count = lf.count, buf = lf.buf;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0)
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
     atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
+    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
+  }
   int rows_per_cta = (count + gridDim.x - 1) / gridDim.x;
   rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
   const int lo = blockIdx.x * rows_per_cta;

@@ -17,12 +17,30 @@ def _chunks(n, start=0):
 
 
 def _assemble(gen_chunk, n, start):
-    xs, ys = [], []
-    for c, lo, hi in _chunks(n, start):
+    # chunks are independent streams: generate them on a thread pool (numpy's generators release the GIL)
+    from concurrent.futures import ThreadPoolExecutor
+    import os
+    spans = list(_chunks(n, start))
+    f = None
+    x_out = y_out = None
+    pos = [0]
+    for _, lo, hi in spans:
+        pos.append(pos[-1] + hi - lo)
+
+    def work(i):
+        c, lo, hi = spans[i]
         x, y = gen_chunk(c)
-        xs.append(x[lo:hi])
-        ys.append(y[lo:hi])
-    return np.concatenate(xs), np.concatenate(ys)
+        return i, x[lo:hi], y[lo:hi]
+
+    with ThreadPoolExecutor(max_workers=min(len(spans), max(1, (os.cpu_count() or 2) - 1))) as ex:
+        for i, x, y in ex.map(work, range(len(spans))):
+            if x_out is None:
+                x_out = np.empty((n, x.shape[1]), dtype=x.dtype)
+                y_out = np.empty(n, dtype=y.dtype)
+            x_out[pos[i]:pos[i + 1]] = x
+            y_out[pos[i]:pos[i + 1]] = y
+    del f
+    return x_out, y_out
 
 
 def higgs_shape(n, start=0, seed=20240601, f=28):
@@ -39,7 +57,8 @@ def higgs_shape(n, start=0, seed=20240601, f=28):
             elif k == 2:
                 x[:, j] = rng.uniform(-np.pi, np.pi, CHUNK)
             else:
-                x[:, j] = rng.choice(np.array([0.0, 1.0865, 2.1731]), CHUNK, p=[0.5, 0.3, 0.2])
+                u = rng.random(CHUNK)
+                x[:, j] = np.where(u < 0.5, 0.0, np.where(u < 0.8, 1.0865, 2.1731))
         z = 0.8 * x[:, 0] - 0.6 * x[:, 1] + 0.5 * np.sin(x[:, 2]) + 0.7 * (x[:, 3] > 1) + 0.3 * x[:, 4] * x[:, 8 % f] - 0.2
         y = (rng.random(CHUNK) < 1.0 / (1.0 + np.exp(-z))).astype(np.float32)
         return x, y

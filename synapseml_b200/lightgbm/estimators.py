@@ -1,0 +1,320 @@
+"""LightGBMClassifier / LightGBMRegressor / LightGBMRanker: the estimator API of the reference with its parameter names
+and defaults (LightGBMParams.scala), over a local stand-in for a Spark DataFrame.
+
+Mirrors LightGBMBase.scala (train :36-65, trainOneDataBatch :396-447, calculateRowStatistics :509-550, getSampledRows
+:724-749, executeTraining :569-606), LightGBMClassifier.scala:27-89, LightGBMRegressor.scala:39-92 and
+LightGBMRanker.scala:26-121.  One process is one executor with one GPU; under torchrun every rank calls fit() with its
+own partitions (rows of rank r precede rows of rank r+1 in the global order).
+"""
+import numpy as np
+
+from . import network_manager as nm
+from .dataset import ReferenceDatasetUtils
+from .model_text import TextModel
+from .params import (CategoricalParams, ClassifierTrainParams, DartModeParams, DatasetParams, ExecutionParams, GeneralParams,
+                     ObjectiveParams, QuantizedGradParams, RankerTrainParams, RegressorTrainParams, SeedParams,
+                     dataset_creation_params)
+from .partition_task import BulkPartitionTask, StreamingPartitionTask
+
+
+class LocalDataFrame:
+    """Stand-in for a Spark DataFrame: a list of partitions, each a dict column -> numpy array."""
+
+    def __init__(self, partitions):
+        self.partitions = list(partitions)
+
+    @staticmethod
+    def from_arrays(features, label, num_partitions=1, **cols):
+        n = len(label)
+        bounds = [n * i // num_partitions for i in range(num_partitions + 1)]
+        parts = []
+        for i in range(num_partitions):
+            b, e = bounds[i], bounds[i + 1]
+            p = {"features": features[b:e], "label": label[b:e]}
+            for k, v in cols.items():
+                if v is not None:
+                    p[k] = v[b:e]
+            parts.append(p)
+        return LocalDataFrame(parts)
+
+    def count(self):
+        return sum(len(p["label"]) for p in self.partitions)
+
+
+# name -> default.  None = "not set": the key is then omitted from the native string and the native default applies
+# (LightGBMBase.scala:249-288 uses get(param), which ignores Spark-side defaults).
+_DEFAULTS = dict(
+    numIterations=100, learningRate=0.1, numLeaves=None, maxBin=None, binSampleCount=None, baggingFraction=None,
+    posBaggingFraction=None, negBaggingFraction=None, baggingFreq=None, baggingSeed=None, earlyStoppingRound=0,
+    improvementTolerance=0.0, featureFraction=None, featureFractionByNode=None, maxDepth=None, minSumHessianInLeaf=None,
+    parallelism="data_parallel", topK=None, verbosity=-1, boostingType="gbdt", lambdaL1=None, lambdaL2=None, metric=None,
+    minGainToSplit=None, maxDeltaStep=None, minDataPerBin=None, minDataInLeaf=None, topRate=None, otherRate=None,
+    isEnableSparse=None, useMissing=None, zeroAsMissing=None, seed=None, deterministic=None, dataRandomSeed=None,
+    passThroughArgs=None, numThreads=None, dataTransferMode="streaming", samplingMode="subset", samplingSubsetSize=1000000,
+    microBatchSize=100, useSingleDatasetMode=True, maxStreamingOMPThreads=16, chunkSize=10000, matrixType="auto",
+    labelCol="label", featuresCol="features", weightCol=None, initScoreCol=None, slotNames=None, referenceDataset=None,
+    useQuantizedGrad=None, numGradQuantBins=None, stochasticRounding=None, isProvideTrainingMetric=None, delegate=None,
+    defaultListenPort=nm.DEFAULT_LOCAL_LISTEN_PORT, timeout=1200.0, modelString=None,
+)
+_SPARK_DEFAULTS = dict(maxBin=255, binSampleCount=200000, minDataInLeaf=20, numLeaves=31)   # values getXxx returns when unset
+
+
+class LightGBMBase:
+    _objective_default = "regression"
+
+    def __init__(self, **kwargs):
+        self._p = dict(_DEFAULTS)
+        self._p["objective"] = self._objective_default
+        self._p.update(self._extra_defaults())
+        for k, v in kwargs.items():
+            self._set(k, v)
+        self.performance_measures = None
+
+    def _extra_defaults(self):
+        return {}
+
+    def _set(self, k, v):
+        if k not in self._p:
+            raise AttributeError("Unknown param %s" % k)
+        if k == "dataTransferMode" and v not in ("streaming", "bulk"):
+            raise ValueError("dataTransferMode must be streaming or bulk")     # TrainingContext.scala:67-69
+        self._p[k] = v
+        return self
+
+    def __getattr__(self, name):
+        if name.startswith("set") and len(name) > 3:
+            key = name[3].lower() + name[4:]
+            if key == "executionMode":           # deprecated alias (LightGBMParams.scala:86-90)
+                key = "dataTransferMode"
+            return lambda v: self._set(key, v)
+        if name.startswith("get") and len(name) > 3:
+            key = name[3].lower() + name[4:]
+            if key == "executionMode":
+                key = "dataTransferMode"
+            return lambda: self._p[key] if self._p.get(key) is not None else _SPARK_DEFAULTS.get(key)
+        raise AttributeError(name)
+
+    # ------------------------------------------------------------------ param groups (LightGBMBase.scala:240-372)
+    def _general_params(self, num_tasks):
+        g = self._p
+        return GeneralParams(parallelism=g["parallelism"], topK=g["topK"], numIterations=g["numIterations"], learningRate=g["learningRate"],
+                             numLeaves=g["numLeaves"], maxBin=g["maxBin"], binSampleCount=g["binSampleCount"],
+                             baggingFraction=g["baggingFraction"], posBaggingFraction=g["posBaggingFraction"],
+                             negBaggingFraction=g["negBaggingFraction"], baggingFreq=g["baggingFreq"], baggingSeed=g["baggingSeed"],
+                             earlyStoppingRound=g["earlyStoppingRound"], improvementTolerance=g["improvementTolerance"],
+                             featureFraction=g["featureFraction"], featureFractionByNode=g["featureFractionByNode"], maxDepth=g["maxDepth"],
+                             minSumHessianInLeaf=g["minSumHessianInLeaf"], numMachines=num_tasks, modelString=g["modelString"],
+                             verbosity=g["verbosity"], boostingType=g["boostingType"], lambdaL1=g["lambdaL1"], lambdaL2=g["lambdaL2"],
+                             metric=g["metric"], minGainToSplit=g["minGainToSplit"], maxDeltaStep=g["maxDeltaStep"],
+                             minDataPerBin=g["minDataPerBin"], minDataInLeaf=g["minDataInLeaf"], topRate=g["topRate"], otherRate=g["otherRate"],
+                             featureNames=list(g["slotNames"] or []))
+
+    def _common_groups(self, num_tasks, num_tasks_per_exec):
+        g = self._p
+        exec_threads = g["numThreads"] if g["numThreads"] is not None else max(num_tasks_per_exec - 1, 0)
+        return dict(
+            passThroughArgs=g["passThroughArgs"], isProvideTrainingMetric=g["isProvideTrainingMetric"], delegate=g["delegate"],
+            generalParams=self._general_params(num_tasks),
+            datasetParams=DatasetParams(g["isEnableSparse"], g["useMissing"], g["zeroAsMissing"]),
+            dartModeParams=DartModeParams(),
+            executionParams=ExecutionParams(g["chunkSize"], g["matrixType"], exec_threads, g["dataTransferMode"], g["samplingMode"],
+                                            g["samplingSubsetSize"], g["microBatchSize"], g["useSingleDatasetMode"], g["maxStreamingOMPThreads"]),
+            objectiveParams=ObjectiveParams(g["objective"], None),
+            seedParams=SeedParams(seed=g["seed"], deterministic=g["deterministic"], dataRandomSeed=g["dataRandomSeed"],
+                                  boostingType=g["boostingType"], objective=g["objective"]),
+            categoricalParams=CategoricalParams(),
+            quantizedParams=QuantizedGradParams(g["useQuantizedGrad"], g["numGradQuantBins"], g["stochasticRounding"]))
+
+    def get_train_params(self, num_tasks, num_tasks_per_exec):
+        raise NotImplementedError
+
+    # ------------------------------------------------------------------ sampling (LightGBMBase.scala:724-749)
+    def get_sampled_rows(self, df, total_num_rows):
+        g = self._p
+        bin_sample_count = self.getBinSampleCount()
+        num_samples = min(bin_sample_count, total_num_rows)
+        mode = g["samplingMode"]
+        feats = [p["features"] for p in df.partitions if len(p["label"])]
+        if mode == "fixed":       # df.limit(numSamples)
+            return np.concatenate(feats)[:num_samples]
+        seed = g["dataRandomSeed"] if g["dataRandomSeed"] is not None else 0
+        fraction = 1.0 if total_num_rows < bin_sample_count else min(1.0, (bin_sample_count + 10000.0) / total_num_rows)
+        rng = np.random.Generator(np.random.PCG64(seed))
+        allx = np.concatenate(feats)
+        if mode == "global":      # sample(fraction, seed).limit(numSamples)
+            keep = rng.random(len(allx)) < fraction
+            return allx[keep][:num_samples]
+        # "subset" (default): limit(samplingSubsetSize).sample(fraction, seed), with samplingSubsetSize capped at numSamples (:733)
+        subset = min(g["samplingSubsetSize"], num_samples)
+        head = allx[:subset]
+        keep = rng.random(len(head)) < fraction
+        return head[keep]
+
+    def preprocess_data(self, df):
+        return df
+
+    # ------------------------------------------------------------------ train
+    def fit(self, df):
+        """LightGBMBase.train -> trainOneDataBatch: row statistics, bin sample -> reference dataset, then the partition task."""
+        import time
+        import torch.distributed as dist
+        g = self._p
+        t_start = time.time()
+        df = self.preprocess_data(df)
+        dist_on = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        rank = dist.get_rank() if dist_on else 0
+        world = dist.get_world_size() if dist_on else 1
+        num_tasks_per_exec = max(1, len(df.partitions))
+        first = next((p for p in df.partitions if len(p["label"])), None)
+        if first is None:
+            raise ValueError("Empty dataset")
+        num_cols = first["features"].shape[1]
+        local_rows = df.count()
+        total_rows = local_rows
+        if dist_on:
+            counts = [None] * world
+            dist.all_gather_object(counts, local_rows)
+            total_rows = int(sum(counts))
+        train_params = self.get_train_params(world, num_tasks_per_exec)
+        ds_params = dataset_creation_params(self.getMaxBin(), self.getBinSampleCount(), self.getMinDataInLeaf(),
+                                            train_params.executionParams.numThreads,
+                                            data_random_seed=g["dataRandomSeed"] if g["dataRandomSeed"] is not None else g["seed"])
+        if g["passThroughArgs"]:
+            ds_params = g["passThroughArgs"] + " " + ds_params
+        measures = {}
+        ctx = dict(train_params=train_params, dataset_params=ds_params, num_cols=num_cols, feature_names=g["slotNames"],
+                   measures=measures, hist_timing=getattr(self, "_hist_timing", False), keep_scores=getattr(self, "_keep_scores", False))
+        if g["dataTransferMode"] == "streaming":
+            serialized = g["referenceDataset"]
+            if serialized is None:
+                t0 = time.time()
+                payload = [None]
+                if rank == 0:     # the driver samples and finds the bin boundaries (K1), everyone else receives the bytes
+                    sampled = self.get_sampled_rows(df, total_rows)
+                    payload[0] = ReferenceDatasetUtils.create_reference_dataset_from_sample(ds_params, g["featuresCol"], total_rows,
+                                                                                            num_cols, sampled)
+                if dist_on:
+                    dist.broadcast_object_list(payload, src=0)
+                serialized = payload[0]
+                measures["samplingTime"] = time.time() - t0
+                self._p["referenceDataset"] = serialized      # cached across fits (LightGBMBase.scala:427-431)
+            ctx["serialized_reference"] = serialized
+            task = StreamingPartitionTask(ctx)
+        else:
+            task = BulkPartitionTask(ctx)
+        ctx["network_info"] = nm.get_global_network_info(g["defaultListenPort"]) if dist_on else None
+        t0 = time.time()
+        model_str = task.run(df.partitions)
+        measures["trainingTime"] = time.time() - t0
+        measures["totalTime"] = time.time() - t_start
+        self.performance_measures = measures
+        if dist_on:
+            payload = [model_str]
+            dist.broadcast_object_list(payload, src=0)
+            model_str = payload[0]
+        return self._make_model(model_str)
+
+    def getPerformanceMeasures(self):
+        return self.performance_measures
+
+    def _make_model(self, model_str):
+        raise NotImplementedError
+
+
+class LightGBMModelBase:
+    def __init__(self, model_str):
+        self.model_str = model_str
+        self._model = TextModel(model_str)
+
+    def getNativeModel(self):
+        return self.model_str
+
+    def saveNativeModel(self, path):
+        with open(path, "w") as f:
+            f.write(self.model_str)
+
+    def predict_raw(self, features):
+        return self._model.predict_raw(features)
+
+    def getFeatureImportances(self, importance_type="split"):
+        imp = np.zeros(self._model.max_feature_idx + 1)
+        for t in self._model.trees:
+            if t.num_leaves > 1:
+                for f, gain in zip(t.split_feature, t.split_gain):
+                    imp[f] += 1 if importance_type == "split" else gain
+        return imp.tolist()
+
+
+class LightGBMClassificationModel(LightGBMModelBase):
+    def transform(self, features):
+        raw = self.predict_raw(features)
+        p = 1.0 / (1.0 + np.exp(-raw))
+        # binary: the native value is the positive-class score; expanded as the reference does (LightGBMBooster.scala:559-575)
+        return dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1), prediction=(p > 0.5).astype(np.float64))
+
+
+class LightGBMRegressionModel(LightGBMModelBase):
+    def transform(self, features):
+        return dict(prediction=self.predict_raw(features))
+
+
+class LightGBMRankerModel(LightGBMModelBase):
+    def transform(self, features):
+        return dict(prediction=self.predict_raw(features))
+
+
+class LightGBMClassifier(LightGBMBase):
+    _objective_default = "binary"          # LightGBMClassifier.scala:35
+
+    def _extra_defaults(self):
+        return dict(isUnbalance=False, boostFromAverage=True)
+
+    def get_train_params(self, num_tasks, num_tasks_per_exec):
+        if self._p["objective"] != "binary":
+            raise NotImplementedError("only objective=binary is built for the classifier (multiclass: later row)")
+        return ClassifierTrainParams(isUnbalance=self._p["isUnbalance"], boostFromAverage=self._p["boostFromAverage"],
+                                     **self._common_groups(num_tasks, num_tasks_per_exec))
+
+    def _make_model(self, model_str):
+        return LightGBMClassificationModel(model_str)
+
+
+class LightGBMRegressor(LightGBMBase):
+    _objective_default = "regression"      # LightGBMRegressor.scala:47
+
+    def _extra_defaults(self):
+        return dict(alpha=0.9, tweedieVariancePower=1.5, boostFromAverage=True)
+
+    def get_train_params(self, num_tasks, num_tasks_per_exec):
+        return RegressorTrainParams(alpha=self._p["alpha"], tweedieVariancePower=self._p["tweedieVariancePower"],
+                                    boostFromAverage=self._p["boostFromAverage"], **self._common_groups(num_tasks, num_tasks_per_exec))
+
+    def _make_model(self, model_str):
+        return LightGBMRegressionModel(model_str)
+
+
+class LightGBMRanker(LightGBMBase):
+    _objective_default = "lambdarank"      # LightGBMRanker.scala:34
+
+    def _extra_defaults(self):
+        return dict(maxPosition=20, labelGain=[], evalAt=[1, 2, 3, 4, 5], groupCol="group")
+
+    def get_train_params(self, num_tasks, num_tasks_per_exec):
+        return RankerTrainParams(maxPosition=self._p["maxPosition"], labelGain=list(self._p["labelGain"]), evalAt=list(self._p["evalAt"]),
+                                 **self._common_groups(num_tasks, num_tasks_per_exec))
+
+    def preprocess_data(self, df):
+        """sortWithinPartitions(groupCol) (LightGBMRanker.scala:88-90); groups must not straddle partitions (:94-120)."""
+        parts = []
+        for p in df.partitions:
+            if "group" not in p:
+                raise ValueError("LightGBMRanker needs a group column")
+            g = np.asarray(p["group"])
+            if g.dtype.kind not in "iuUSO":
+                raise ValueError("group column must be int, long or string")
+            order = np.argsort(g, kind="stable")
+            parts.append({k: (np.asarray(v)[order] if k != "_gid" else v) for k, v in p.items()})
+        return LocalDataFrame(parts)
+
+    def _make_model(self, model_str):
+        return LightGBMRankerModel(model_str)

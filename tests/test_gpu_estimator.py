@@ -1,0 +1,109 @@
+"""Estimator API (the reference's user-facing surface) on the GPU: behaviours the reference's own suites assert."""
+import numpy as np
+import pytest
+
+from synapseml_b200.data import synthetic as S
+from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LightGBMRanker, LightGBMRegressor, LocalDataFrame
+
+pytestmark = pytest.mark.gpu
+
+
+def auc(y, p):
+    order = np.argsort(p, kind="stable")
+    r = np.empty(len(p))
+    r[order] = np.arange(1, len(p) + 1)
+    pos = y > 0
+    return (r[pos].sum() - pos.sum() * (pos.sum() + 1) / 2) / (pos.sum() * (~pos).sum())
+
+
+def test_classifier_fits_and_scores(native):
+    X, y = S.higgs_shape(60000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)            # numPartitions = 2, LightGBMTestUtils.scala:95
+    model = LightGBMClassifier(numIterations=10, numLeaves=5).fit(df)   # the reference's benchmark setting (10 iters, 5 leaves)
+    out = model.transform(X)
+    assert auc(y, out["probability"][:, 1]) > 0.72
+    assert out["rawPrediction"].shape == (len(y), 2) and np.allclose(out["rawPrediction"][:, 0], -out["rawPrediction"][:, 1])
+    assert "is_unbalance: false" in model.getNativeModel() and "[learning_rate: 0.1]" in model.getNativeModel()
+
+
+def test_streaming_and_bulk_give_the_same_model(native):
+    # the reference re-runs its streaming suites in bulk mode by subclass override (SURVEY.md §4 "mode matrix")
+    X, y = S.higgs_shape(30000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=3)
+    kw = dict(numIterations=5, numLeaves=15, useQuantizedGrad=True, stochasticRounding=False, samplingMode="fixed")
+    a = LightGBMClassifier(dataTransferMode="streaming", **kw).fit(df).getNativeModel().split("parameters:")[0]
+    b = LightGBMClassifier(dataTransferMode="bulk", **kw).fit(df).getNativeModel().split("parameters:")[0]
+    assert a == b
+
+
+def test_micro_batch_size_invariance_and_threaded_push(native):
+    # VerifyLightGBMClassifierStream.scala:395-405 (chunk size invariance)
+    X, y = S.higgs_shape(20000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=4)
+    kw = dict(numIterations=4, numLeaves=15, useQuantizedGrad=True, stochasticRounding=False, samplingMode="fixed")
+    models = [LightGBMClassifier(microBatchSize=mb, **kw).fit(df).getNativeModel() for mb in (1, 100, 4096)]
+    assert models[0] == models[1] == models[2]
+
+
+def test_reference_dataset_reuse_gives_identical_model_string(native):
+    # VerifyLightGBMClassifierStreamOnly.scala:44-56
+    X, y = S.higgs_shape(20000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    est = LightGBMClassifier(numIterations=4, numLeaves=15, samplingMode="fixed")
+    m1 = est.fit(df)
+    assert est.getReferenceDataset() is not None
+    est2 = LightGBMClassifier(numIterations=4, numLeaves=15, samplingMode="fixed", referenceDataset=est.getReferenceDataset())
+    assert est2.fit(df).getNativeModel() == m1.getNativeModel()
+
+
+def test_determinism(native):
+    # VerifyLightGBMClassifierStream.scala:95-101 (same input -> same result, 1e-10); here: identical model strings,
+    # float mode included, because histograms are integer sums in every mode
+    X, y = S.higgs_shape(50000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    ms = [LightGBMClassifier(numIterations=6, seed=1, deterministic=True).fit(df).getNativeModel() for _ in range(3)]
+    assert ms[0] == ms[1] == ms[2]
+
+
+def test_empty_partition_and_sampling_modes(native):
+    # VerifyLightGBMClassifierStream.scala:449-461 and VerifyLightGBMClassifierStreamOnly.scala:12-42
+    X, y = S.higgs_shape(12000)
+    parts = LocalDataFrame.from_arrays(X, y, num_partitions=2).partitions
+    parts.insert(1, {"features": X[:0], "label": y[:0]})
+    for mode in ("global", "fixed", "subset"):
+        m = LightGBMClassifier(numIterations=3, numLeaves=7, samplingMode=mode).fit(LocalDataFrame(parts))
+        assert len(m._model.trees) == 3
+
+
+def test_regressor_and_weight_column(native):
+    X, y = S.dense100(30000, f=20)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    m = LightGBMRegressor(numIterations=20, numLeaves=15).fit(df)
+    rmse0 = np.sqrt(np.mean((y - y.mean()) ** 2))
+    rmse = np.sqrt(np.mean((y - m.transform(X)["prediction"]) ** 2))
+    assert rmse < 0.6 * rmse0
+    # a weight column that favours large labels shifts the mean prediction up (VerifyLightGBMRegressorStream "weight column")
+    w = np.where(y > np.median(y), 10.0, 0.1).astype(np.float32)
+    mw = LightGBMRegressor(numIterations=20, numLeaves=15).fit(LocalDataFrame.from_arrays(X, y, num_partitions=2, weight=w))
+    assert mw.transform(X)["prediction"].mean() > m.transform(X)["prediction"].mean()
+
+
+def test_ranker_group_column_types(native):
+    # VerifyLightGBMRankerStream.scala:22-74: group column as int, long and string; rejects a double group column
+    X, rel, qid = S.mslr_shape(12000, f=20)
+    ms = []
+    for conv in (lambda q: q.astype(np.int32), lambda q: q.astype(np.int64) + (1 << 40), lambda q: np.array(["q%06d" % v for v in q])):
+        df = LocalDataFrame.from_arrays(X, rel, num_partitions=1, group=conv(qid))
+        ms.append(LightGBMRanker(numIterations=4, numLeaves=15, minDataInLeaf=10).fit(df).getNativeModel())
+    assert ms[0] == ms[1] == ms[2]
+    with pytest.raises(ValueError):
+        LightGBMRanker(numIterations=1).fit(LocalDataFrame.from_arrays(X, rel, num_partitions=1, group=qid.astype(np.float64)))
+
+
+def test_unsupported_options_fail_loudly(native):
+    X, y = S.higgs_shape(2000)
+    df = LocalDataFrame.from_arrays(X, y)
+    from synapseml_b200.lightgbm.native import LightGBMNativeError
+    for kw in (dict(boostingType="dart"), dict(zeroAsMissing=True), dict(maxBin=1000)):
+        with pytest.raises((LightGBMNativeError, NotImplementedError)):
+            LightGBMClassifier(numIterations=1, **kw).fit(df)

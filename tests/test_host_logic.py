@@ -1,0 +1,104 @@
+"""Host-side mirror of the reference's Scala layer: the pure-logic known answers the reference itself tests."""
+import numpy as np
+import pytest
+
+from synapseml_b200.lightgbm.dataset import GroupIdManager, SampledData, count_cardinality
+from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LightGBMRanker, LightGBMRegressor, LocalDataFrame
+from synapseml_b200.lightgbm.params import (ClassifierTrainParams, GeneralParams, ObjectiveParams, ParamsStringBuilder,
+                                            QuantizedGradParams, RankerTrainParams, dataset_creation_params)
+
+
+def test_count_cardinality_reference_vector():
+    # lightgbm/src/test/scala/.../split2/VerifyLightGBMRankerStream.scala:76-89
+    assert count_cardinality([1, 1, 2, 2, 2, 3]) == [2, 3, 1]
+    assert count_cardinality([1 << 40, 1 << 40, 2, 2, 2, 3]) == [2, 3, 1]
+    assert count_cardinality(["a", "a", "b", "b", "b", "c"]) == [2, 3, 1]
+
+
+def test_params_string_builder_append_if_not_there():
+    # core/src/test/scala/.../core/utils/VerifyParamsStringBuilder.scala
+    sb = ParamsStringBuilder(prefix="--", delimiter=" ")
+    sb.append("--first_param 1").append_param_value_if_not_there("first_param", 2).append_param_value_if_not_there("second", 3.5)
+    sb.append_param_flag_if_not_there("flag").append_param_flag_if_not_there("flag")
+    sb.append_param_list_if_not_there("lst", [1, 2, 3]).append_param_value_if_not_there("none", None)
+    assert sb.result() == "--first_param 1 --second 3.5 --flag --lst 1,2,3"
+
+
+def test_booster_param_string_first_writer_wins():
+    p = ClassifierTrainParams(passThroughArgs="max_bin=63 learning_rate=0.3",
+                              generalParams=GeneralParams(numLeaves=31, maxBin=255, learningRate=0.1, minSumHessianInLeaf=1e-4, numIterations=7),
+                              objectiveParams=ObjectiveParams("binary"), quantizedParams=QuantizedGradParams(True))
+    s = p.to_string()
+    assert s.startswith("max_bin=63 learning_rate=0.3 is_pre_partition=True boosting_type=gbdt tree_learner=data_parallel num_leaves=31")
+    assert s.count("max_bin=") == 1 and s.count("learning_rate=") == 1
+    assert "min_sum_hessian_in_leaf=1.0E-4" in s          # JVM Double.toString
+    assert "num_iterations=7" in s and "objective=binary" in s and "use_quantized_grad=true" in s
+    assert s.endswith("is_unbalance=false boost_from_average=true")
+    r = RankerTrainParams(objectiveParams=ObjectiveParams("lambdarank")).to_string()
+    assert r.endswith("eval_at=1,2,3,4,5 max_position=20")
+
+
+def test_dataset_creation_params():
+    assert dataset_creation_params(255, 200000, 20, 7) == "is_pre_partition=True max_bin=255 bin_construct_sample_cnt=200000 min_data_in_leaf=20 num_threads=7"
+    assert dataset_creation_params(255, 200000, 20, 7, data_random_seed=3).endswith("data_random_seed=3")
+
+
+def test_sampled_data_layout():
+    # SampledData.scala:43-77: column-major, zeros skipped, NaN kept, row index recorded
+    rows = np.array([[0.0, 1.5, np.nan], [2.0, 0.0, 0.0], [3.0, 0.0, 4.0]])
+    sd = SampledData(3, 3)
+    for i, r in enumerate(rows):
+        sd.push_row(r, i)
+    assert sd.row_counts.tolist() == [2, 1, 2]
+    assert sd.sample_data[0][:2].tolist() == [2.0, 3.0] and sd.sample_indexes[0][:2].tolist() == [1, 2]
+    assert sd.sample_data[1][:1].tolist() == [1.5] and sd.sample_indexes[1][:1].tolist() == [0]
+    assert np.isnan(sd.sample_data[2][0]) and sd.sample_data[2][1] == 4.0 and sd.sample_indexes[2][:2].tolist() == [0, 2]
+    sd2 = SampledData(3, 3)
+    sd2.push_rows(rows)
+    assert sd2.row_counts.tolist() == sd.row_counts.tolist()
+    for j in range(3):
+        k = sd.row_counts[j]
+        assert np.array_equal(sd.sample_data[j][:k], sd2.sample_data[j][:k], equal_nan=True)
+        assert np.array_equal(sd.sample_indexes[j][:k], sd2.sample_indexes[j][:k])
+
+
+def test_group_id_manager():
+    g = GroupIdManager()
+    assert [g.get_unique_index_for_id(v) for v in ["q7", "q7", "q2", "q7", 5]] == [0, 0, 1, 0, 2]
+
+
+def test_estimator_params_and_defaults():
+    c = LightGBMClassifier().setNumLeaves(15).setExecutionMode("bulk").setUseQuantizedGrad(True)
+    assert c.getNumLeaves() == 15 and c.getDataTransferMode() == "bulk" and c.getMaxBin() == 255 and c.getObjective() == "binary"
+    assert c.getNumIterations() == 100 and c.getLearningRate() == 0.1 and c.getMinDataInLeaf() == 20
+    s = c.get_train_params(1, 4).to_string()
+    assert "num_leaves=15" in s and "max_bin" not in s and "num_threads=3" in s and "use_quantized_grad=true" in s
+    assert LightGBMRegressor().getObjective() == "regression" and LightGBMRanker().getObjective() == "lambdarank"
+    assert LightGBMRanker().getMaxPosition() == 20
+    with pytest.raises(ValueError):
+        LightGBMClassifier().setDataTransferMode("neither")
+    with pytest.raises(AttributeError):
+        LightGBMClassifier().setNoSuchParam(1)
+
+
+def test_sampling_modes():
+    X = np.arange(50000 * 2, dtype=np.float64).reshape(50000, 2)
+    df = LocalDataFrame.from_arrays(X, np.zeros(50000), num_partitions=3)
+    est = LightGBMClassifier(binSampleCount=1000, samplingMode="fixed")
+    assert np.array_equal(est.get_sampled_rows(df, 50000), X[:1000])
+    est = LightGBMClassifier(binSampleCount=1000, samplingMode="global")
+    s = est.get_sampled_rows(df, 50000)
+    assert len(s) == 1000
+    # "subset": limit(min(samplingSubsetSize, numSamples)).sample(fraction) with no final limit -> ~fraction * 1000 rows
+    est = LightGBMClassifier(binSampleCount=1000, samplingMode="subset")
+    s = est.get_sampled_rows(df, 50000)
+    assert 150 < len(s) < 300 and s[:, 0].max() < 2000
+
+
+def test_ranker_sorts_within_partitions_and_rejects_bad_group_column():
+    df = LocalDataFrame([{"features": np.arange(8.0).reshape(4, 2), "label": np.arange(4.0), "group": np.array([3, 1, 3, 1])}])
+    out = LightGBMRanker().preprocess_data(df).partitions[0]
+    assert out["group"].tolist() == [1, 1, 3, 3] and out["label"].tolist() == [1.0, 3.0, 0.0, 2.0]
+    bad = LocalDataFrame([{"features": np.zeros((2, 2)), "label": np.zeros(2), "group": np.array([0.5, 1.5])}])
+    with pytest.raises(ValueError):
+        LightGBMRanker().preprocess_data(bad)
