@@ -18,7 +18,7 @@ template <typename K>
 void SetSmem(K kernel, size_t bytes) {
   LGB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
 }
-constexpr size_t kHistSmem = size_t(4) * kBins * 32 * sizeof(unsigned int);   // 128 KB in both modes
+constexpr size_t kHistSmem = kHistSmemBytes;   // 4 x 32 KB arrays + 32 KB alignment slack, both modes
 }  // namespace
 
 Booster::Booster(Dataset* train, const char* params) : ds_(train) {
@@ -80,7 +80,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   d_leaves_.AllocZero(L);
   d_ctrl_.AllocZero(1);
   d_feat_best_.Alloc(static_cast<size_t>(2) * std::max(F_, 1));
-  d_splittable_.Alloc(static_cast<size_t>(L) * std::max(F_, 1));
+  d_splittable_.Alloc(static_cast<size_t>(L + 2) * std::max(F_, 1));   // + 2 scratch rows (k_find)
   d_sorted_leaf_.AllocZero(2 * L);
   // tree arrays blob: 8 int arrays [L], decision_type [L], split_gain [L], 4 double arrays [L]
   {
@@ -98,8 +98,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
   }
-  SetSmem(k_hist<4, 4, false>, kHistSmem); SetSmem(k_hist<2, 4, false>, kHistSmem); SetSmem(k_hist<1, 4, false>, kHistSmem);
-  SetSmem(k_hist<4, 2, true>, kHistSmem); SetSmem(k_hist<2, 2, true>, kHistSmem); SetSmem(k_hist<1, 2, true>, kHistSmem);
+#define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_hist<RR, BPL, FLT, false>, kHistSmem)
+  SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
+  SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
+#undef SET_HIST_SMEM
   LGB_CUDA(cudaStreamSynchronize(stream_));
 }
 
@@ -259,7 +261,8 @@ void Booster::LaunchHist(bool root) {
     const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
     rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
   }
-  LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, d_hist_work_.bytes(), stream_));
+  // non-root launches find `work` already cleared by k_part_scatter
+  if (root) LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, d_hist_work_.bytes(), stream_));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (time_hist_) {
     if (hist_events_used_ == hist_events_.size()) {
@@ -271,22 +274,39 @@ void Booster::LaunchHist(bool root) {
     ++hist_events_used_;
     LGB_CUDA(cudaEventRecord(e0, stream_));
   }
-#define LAUNCH_HIST(RR, BPL, FLT)                                                                                      \
-  k_hist<RR, BPL, FLT><<<grid, kHistThreads, kHistSmem, stream_>>>(ds_->d_rm.p, lay.rm_stride, d_gh16_.p, d_ghfix_.p,   \
-                                                                   d_idx_[0].p, d_idx_[1].p, d_leaves_.p, d_ctrl_.p,    \
-                                                                   d_hist_work_.p, F_, root ? 1 : 0, rows_per_flush)
+#define LAUNCH_HIST_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, d_idx_[0].p, d_idx_[1].p, \
+                         d_leaves_.p, d_ctrl_.p, d_hist_work_.p, F_, rows_per_flush
+#define LAUNCH_HIST(RR, BPL, FLT)                                                                              \
+  do {                                                                                                         \
+    if (root) k_hist<RR, BPL, FLT, true><<<grid, kHistThreads, kHistSmem, stream_>>>(LAUNCH_HIST_ARGS);        \
+    else k_hist<RR, BPL, FLT, false><<<grid, kHistThreads, kHistSmem, stream_>>>(LAUNCH_HIST_ARGS);            \
+  } while (0)
   if (!flt) {
     if (R == 4) LAUNCH_HIST(4, 4, false); else if (R == 2) LAUNCH_HIST(2, 4, false); else LAUNCH_HIST(1, 4, false);
   } else {
     if (R == 4) LAUNCH_HIST(4, 2, true); else if (R == 2) LAUNCH_HIST(2, 2, true); else LAUNCH_HIST(1, 2, true);
   }
 #undef LAUNCH_HIST
+#undef LAUNCH_HIST_ARGS
   LGB_CUDA(cudaGetLastError());
   if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
   ++launches_;
   if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, d_hist_work_.n, stream_);
 }
 
+void Booster::LaunchFind(bool root) {
+  dim3 grid(F_, root ? 1 : 2);
+  if (lp_.quantized)
+    k_find<true><<<grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p,
+                                            d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+  else
+    k_find<false><<<grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p,
+                                             d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+  ++launches_;
+}
+
+// One tree = a fixed sequence of launches with device-resident control flow (no host round trip until the tree is read back):
+//   root: hist -> find(+select);  per split: part_count -> part_scatter -> hist(smaller child) -> find(+select)
 void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
@@ -294,22 +314,17 @@ void Booster::TrainTree(HostTree* out) {
   k_tree_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
-  const int find_grid = CeilDiv(F_, 8);
   LaunchHist(true);
-  if (lp_.quantized) k_find<true><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 1);
-  else k_find<false><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 1);
-  ++launches_;
+  LaunchFind(true);
   for (int split = 0; split < L - 1; ++split) {
-    k_select<<<1, 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, d_feat_best_.p, tree_dev_, ds_->d_fmeta.p, lp_);
     k_part_count<<<kPartBlocks, kPartThreads, 0, stream_>>>(ds_->d_cm.p, ds_->n_pad, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
     k_part_scatter<<<kPartBlocks, kPartThreads, 0, stream_>>>(d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_leaves_.p,
-                                                              d_flags_.p, d_part_counts_.p, tree_dev_, d_splittable_.p, lp_);
-    launches_ += 3;
+                                                              d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p,
+                                                              static_cast<int>(d_hist_work_.n), lp_);
+    launches_ += 2;
     if (split < L - 2) {
       LaunchHist(false);
-      if (lp_.quantized) k_find<true><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 0);
-      else k_find<false><<<find_grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p, d_splittable_.p, lp_, 0);
-      ++launches_;
+      LaunchFind(false);
     }
   }
   LGB_CUDA(cudaGetLastError());

@@ -43,6 +43,8 @@ struct TreeCtrl {
   int src_begin, src_count, src_buf;
   int smaller, larger, find, pending;
   int parent_slot;
+  int find_count[2];                // CTAs of k_find that finished, per child (last-CTA reductions)
+  int find_children_done;
   unsigned int max_abs_g_bits, max_abs_h_bits;
   double grad_scale, hess_scale;      // quantized: int -> float scales.  float mode: fixed-point -> float (powers of two)
   double inv_grad_scale, inv_hess_scale;
@@ -146,6 +148,7 @@ class Booster {
   void PrepareGradients();           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
+  void LaunchFind(bool root);
   void FetchTree(HostTree* out);
   void UpdateScores();
   ModelHeader MakeHeader() const;

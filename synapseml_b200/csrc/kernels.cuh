@@ -262,22 +262,51 @@ __global__ void k_quantize(const float* __restrict__ grad, const float* __restri
 // 0.7-3.5 T/s for a [feature][bin] layout; profiles/r01_smem_atomics_microbench.log).  A lane covers BPL consecutive
 // feature bytes of one row; 32/R lanes cover one row record slice and R rows are handled per warp step, so each
 // feature has R private sub-histograms that are summed when the CTA flushes to the global int64 histogram.
-//   quantized: one ATOMS.ADD.U32 per (row, feature) on a packed (grad << 16) + hess word; a CTA flushes before any
+//   quantized: one RED.SHARED.ADD.U32 per (row, feature) on a packed (grad << 16) + hess word; a CTA flushes before any
 //              16-bit lane can overflow.
-//   float    : two ATOMS.ADD.U32 per (row, feature) on 32-bit fixed-point sums.
+//   float    : two RED.SHARED.ADD.U32 per (row, feature) on 32-bit fixed-point sums.
+// The four 32 KB arrays start at a 32 KB-aligned shared address, so the address of an update is
+// ((bins >> s) & 0x7f80) | lane_address — two ALU instructions per atomic.
 // Algorithmic bytes per row visit: F * 1 (bins) + 2 (quantized g,h) or 8 (float) + 4 (row index; 0 at the root).
-template <int R, int BPL, bool FLT>
+constexpr unsigned kHistArrayBytes = kBins * 32 * 4;       // 32 KB
+constexpr size_t kHistSmemBytes = 4 * kHistArrayBytes + kHistArrayBytes;   // + alignment slack
+
+// All of a lane's BPL updates for one row in one asm block: no per-update branch, array offsets as immediates.
+template <int BPL, bool FLT>
+__device__ __forceinline__ void HistUpdate(unsigned bins, unsigned lane_addr, unsigned pk, unsigned gx, unsigned hx) {
+  // byte k of `bins` -> byte offset bin * 128 inside array k
+  const unsigned a0 = ((bins << 7) & 0x7f80u) | lane_addr;
+  const unsigned a1 = ((bins >> 1) & 0x7f80u) | lane_addr;
+  if (FLT) {
+    asm volatile(
+        "red.shared.add.u32 [%0], %2;\n\t"
+        "red.shared.add.u32 [%0+32768], %3;\n\t"
+        "red.shared.add.u32 [%1+65536], %2;\n\t"
+        "red.shared.add.u32 [%1+98304], %3;" ::"r"(a0), "r"(a1), "r"(gx), "r"(hx) : "memory");
+  } else {
+    const unsigned a2 = ((bins >> 9) & 0x7f80u) | lane_addr;
+    const unsigned a3 = ((bins >> 17) & 0x7f80u) | lane_addr;
+    asm volatile(
+        "red.shared.add.u32 [%0], %4;\n\t"
+        "red.shared.add.u32 [%1+32768], %4;\n\t"
+        "red.shared.add.u32 [%2+65536], %4;\n\t"
+        "red.shared.add.u32 [%3+98304], %4;" ::"r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(pk) : "memory");
+  }
+}
+
+template <int R, int BPL, bool FLT, bool ROOT>
 __global__ void __launch_bounds__(kHistThreads, 1)
-k_hist(const uint8_t* __restrict__ rm, int rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
        const int* __restrict__ idx0, const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
-       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int root, int rows_per_flush) {
-  extern __shared__ unsigned int hsm[];
+       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int rows_per_flush) {
+  extern __shared__ unsigned int hsm_raw[];
   constexpr int LPR = 32 / R;                 // lanes per row
   constexpr int FT = LPR * BPL;               // features per tile
-  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays
+  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays (always 4)
+  static_assert(NARR == 4, "four 32 KB arrays");
   if (ctrl->done) return;
-  if (!root && !ctrl->find) return;
-  const LeafDev& lf = leaves[root ? 0 : ctrl->smaller];
+  if (!ROOT && !ctrl->find) return;
+  const LeafDev& lf = leaves[ROOT ? 0 : ctrl->smaller];
   const int begin = lf.begin, count = lf.count, buf = lf.buf;
   if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
     atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
@@ -288,67 +317,77 @@ k_hist(const uint8_t* __restrict__ rm, int rm_stride, const uint16_t* __restrict
   const int lo = blockIdx.x * rows_per_cta;
   const int hi = min(count, lo + rows_per_cta);
   if (lo >= hi) return;
-  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
+  const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int q = lane % LPR, r = lane / LPR;
   const int tile = blockIdx.y;
-  const size_t col_off = static_cast<size_t>(tile) * FT + q * BPL;
+  // 32 KB-aligned window inside the dynamic shared memory
+  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
+  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
+  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
+  const unsigned lane_addr = sbase + lane * 4;
+  // A lane works if its first feature byte is a real feature.  When F is not a multiple of BPL the last working lane also
+  // updates its zero-padded bytes (bin 0 of features >= F), which the flush ignores.
+  const bool kmask = (tile * FT + q * BPL) < F;
+  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + q * BPL;
   for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
   __syncthreads();
-  unsigned int* my = hsm + lane;
+  constexpr int STEPS = 32 / R;
+  constexpr int U = 8;
   for (int sub = lo; sub < hi; sub += rows_per_flush) {
     const int sub_hi = min(hi, sub + rows_per_flush);
     for (int p0 = sub + warp * 32; p0 < sub_hi; p0 += nwarps * 32) {
       const int p = p0 + lane;
       const bool v = p < sub_hi;
       int row_l = -1;
-      if (v) row_l = idx ? idx[begin + p] : begin + p;
-      unsigned int pk_l = 0; int gx_l = 0, hx_l = 0;
+      if (v) row_l = ROOT ? begin + p : idx[begin + p];
+      unsigned pk_l = 0, gx_l = 0, hx_l = 0;
       if (v) {
-        if (FLT) { const int2 t = ghfix[row_l]; gx_l = t.x; hx_l = t.y; }
+        if (FLT) { const int2 t = ghfix[row_l]; gx_l = static_cast<unsigned>(t.x); hx_l = static_cast<unsigned>(t.y); }
         else {
-          const unsigned int w = gh16[row_l];
-          pk_l = (static_cast<unsigned int>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+          const unsigned w = gh16[row_l];
+          pk_l = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
         }
       }
-      constexpr int STEPS = 32 / R;
-      constexpr int U = STEPS < 8 ? STEPS : 8;
-      #pragma unroll 1
-      for (int s0 = 0; s0 < STEPS; s0 += U) {
-        int rows[U]; unsigned int bins[U];
-        #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          rows[u] = __shfl_sync(0xffffffffu, row_l, (s0 + u) * R + r);
-          bins[u] = 0;
-          if (rows[u] >= 0) {
-            const uint8_t* src = rm + static_cast<size_t>(rows[u]) * rm_stride + col_off;
-            if (BPL == 4) bins[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
-            else bins[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
+      if (p0 + 32 <= sub_hi) {
+        // full group of 32 rows: no per-row predicates
+        #pragma unroll 1
+        for (int s0 = 0; s0 < STEPS; s0 += U) {
+          unsigned bins[U];
+          #pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int srcl = (s0 + u) * R + r;
+            const unsigned row = ROOT ? static_cast<unsigned>(begin + p0 + srcl) : static_cast<unsigned>(__shfl_sync(0xffffffffu, row_l, srcl));
+            bins[u] = 0;
+            if (kmask) {
+              const uint8_t* src = rmc + static_cast<size_t>(row) * rm_stride;
+              if (BPL == 4) bins[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
+              else bins[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
+            }
+          }
+          #pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int srcl = (s0 + u) * R + r;
+            unsigned pk = 0, gx = 0, hx = 0;
+            if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
+            else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
+            if (kmask) HistUpdate<BPL, FLT>(bins[u], lane_addr, pk, gx, hx);
           }
         }
-        #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int srcl = (s0 + u) * R + r;
-          if (FLT) {
-            const int gx = __shfl_sync(0xffffffffu, gx_l, srcl);
-            const int hx = __shfl_sync(0xffffffffu, hx_l, srcl);
-            if (rows[u] >= 0) {
-              #pragma unroll
-              for (int k = 0; k < BPL; ++k) {
-                const unsigned int bin = (bins[u] >> (8 * k)) & 0xffu;
-                atomicAdd(my + (2 * k) * (kBins * 32) + bin * 32, static_cast<unsigned int>(gx));
-                atomicAdd(my + (2 * k + 1) * (kBins * 32) + bin * 32, static_cast<unsigned int>(hx));
-              }
-            }
-          } else {
-            const unsigned int pk = __shfl_sync(0xffffffffu, pk_l, srcl);
-            if (rows[u] >= 0) {
-              #pragma unroll
-              for (int k = 0; k < BPL; ++k) {
-                const unsigned int bin = (bins[u] >> (8 * k)) & 0xffu;
-                atomicAdd(my + k * (kBins * 32) + bin * 32, pk);
-              }
-            }
+      } else {
+        #pragma unroll 1
+        for (int s = 0; s < STEPS; ++s) {
+          const int srcl = s * R + r;
+          const int row = __shfl_sync(0xffffffffu, row_l, srcl);
+          unsigned pk = 0, gx = 0, hx = 0;
+          if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
+          else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
+          if (row >= 0 && kmask) {
+            const uint8_t* src = rmc + static_cast<size_t>(static_cast<unsigned>(row)) * rm_stride;
+            unsigned b;
+            if (BPL == 4) b = __ldg(reinterpret_cast<const unsigned int*>(src));
+            else b = __ldg(reinterpret_cast<const unsigned short*>(src));
+            HistUpdate<BPL, FLT>(b, lane_addr, pk, gx, hx);
           }
         }
       }
@@ -386,9 +425,8 @@ k_hist(const uint8_t* __restrict__ rm, int rm_stride, const uint16_t* __restrict
   }
 }
 
-// ------------------------------------------------------------------------------------------------ K5 + K6 split search
-struct GainParams { double l1, l2, max_delta_step; };
 
+// ------------------------------------------------------------------------------------------------ K5 + K6 split search
 __device__ __forceinline__ double ThresholdL1D(double s, double l1) {
   double reg = fabs(s) - l1;
   if (reg < 0.0) reg = 0.0;
@@ -412,9 +450,31 @@ __device__ __forceinline__ double SplitGainD(double lg, double lh, double rg, do
   return LeafGainD(lg, lh, p) + LeafGainD(rg, rh, p);
 }
 
-struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right for reverse, left for forward)
+__device__ __forceinline__ bool SplitBetter(double ga, int fa, double gb, int fb) {
+  // upstream SplitInfo::operator>: larger gain; equal gain -> smaller real feature index (-1 = +inf)
+  const int a = fa < 0 ? 0x7fffffff : fa, b = fb < 0 ? 0x7fffffff : fb;
+  if (ga != gb) return ga > gb;
+  return a < b;
+}
 
-__device__ __forceinline__ Cand WarpBestCand(Cand c, bool prefer_larger_b) {
+__device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
+  SplitDev s;
+  s.gain = KMINSCORE; s.feature = f; s.real_feature = real; s.threshold = 0; s.default_left = 1;
+  s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
+  s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
+  s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
+  return s;
+}
+
+struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right: reverse, left: forward)
+
+// block-wide argmax of candidates; ties on gain go to the larger (reverse scan) or smaller (forward scan) bin, which is
+// what a sequential scan with a strict '>' keeps
+__device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand* s_c /*[8]*/) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  auto better = [&](const Cand& t, const Cand& cur) {
+    return (t.gain > cur.gain) || (t.gain == cur.gain && t.b >= 0 && (cur.b < 0 || (prefer_larger_b ? t.b > cur.b : t.b < cur.b)));
+  };
   for (int o = 16; o > 0; o >>= 1) {
     Cand t;
     t.gain = __shfl_xor_sync(0xffffffffu, c.gain, o);
@@ -422,26 +482,49 @@ __device__ __forceinline__ Cand WarpBestCand(Cand c, bool prefer_larger_b) {
     t.sg = __shfl_xor_sync(0xffffffffu, c.sg, o);
     t.sh = __shfl_xor_sync(0xffffffffu, c.sh, o);
     t.cnt = __shfl_xor_sync(0xffffffffu, c.cnt, o);
-    const bool better = (t.gain > c.gain) || (t.gain == c.gain && t.b >= 0 && (c.b < 0 || (prefer_larger_b ? t.b > c.b : t.b < c.b)));
-    if (better) c = t;
+    if (better(t, c)) c = t;
   }
-  return c;
+  __syncthreads();
+  if (lane == 0) s_c[warp] = c;
+  __syncthreads();
+  Cand r = s_c[0];
+  #pragma unroll
+  for (int w = 1; w < 8; ++w) if (better(s_c[w], r)) r = s_c[w];
+  return r;
 }
 
-// One warp searches one feature of one leaf.  gz/hz: this lane's 8 bins (bins lane*8 .. lane*8+7), already the leaf's
-// histogram.  Implements FindBestThresholdSequentially / ...Int (reverse scan, plus forward scan when the feature has a
-// NaN bin and more than two bins) as prefix sums: the sequential `continue`/`break` conditions are monotone in the scan
-// position, so they reduce to per-threshold predicates.
+// One 256-thread CTA searches one feature of one leaf, one bin per thread.  Implements FindBestThresholdSequentially /
+// ...Int (reverse scan, plus a forward scan when the feature has a NaN bin and more than two bins) with block-wide prefix
+// sums: the sequential `continue` / `break` conditions are monotone in the scan position, so they become per-threshold
+// predicates.  g_in/h_in: this thread's bin of the leaf's histogram.  Result valid in thread 0.
 template <bool QUANT>
-__device__ void WarpFindBest(const long long (&gz_in)[8], const long long (&hz_in)[8], const FeatureMetaDev fm, int f,
-                             long long tot_g, long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data,
-                             const LearnerParams& P, double gscale, double hscale, SplitDev* out, unsigned char* splittable_out) {
-  const int lane = threadIdx.x & 31;
+__device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
+                              long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
+                              double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
+                              long long* out_tot_g, long long* out_tot_h) {
+  __shared__ long long s_g[8], s_h[8];
+  __shared__ int s_c[8];
+  __shared__ Cand s_cand[8];
+  __shared__ int s_flag;
+  const int b = threadIdx.x, lane = b & 31, warp = b >> 5;
   const int num_bin = fm.num_bin;
   const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
   const int nan_bin = two_scans ? num_bin - 1 : -1;
-  long long gz[8], hz[8];
-  int cz[8];
+  if (b == 0) s_flag = 0;
+  // pass 0 (root only): leaf totals = sum of all bins of this feature
+  if (root) {
+    long long tg = g_in, th = h_in;
+    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
+    if (lane == 0) { s_g[warp] = tg; s_h[warp] = th; }
+    __syncthreads();
+    tot_g = 0; tot_h = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) { tot_g += s_g[w]; tot_h += s_h[w]; }
+    leaf_sum_g = static_cast<double>(tot_g) * gscale;
+    leaf_sum_h = static_cast<double>(tot_h) * hscale;
+    __syncthreads();
+  }
+  *out_tot_g = tot_g; *out_tot_h = tot_h;
   double sum_gradient, sum_hessian, cnt_factor;
   if (QUANT) {
     sum_gradient = static_cast<double>(tot_g) * gscale;
@@ -452,115 +535,88 @@ __device__ void WarpFindBest(const long long (&gz_in)[8], const long long (&hz_i
     sum_hessian = leaf_sum_h + 2 * KEPS;
     cnt_factor = num_data / sum_hessian;
   }
-  // inclusive prefix sums over bins, NaN bin (when scanned separately) and bins >= num_bin zeroed
-  long long pg = 0, ph = 0; int pc = 0;
-  #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int b = lane * 8 + j;
-    const bool use = b < num_bin && b != nan_bin;
-    gz[j] = use ? gz_in[j] : 0; hz[j] = use ? hz_in[j] : 0;
-    cz[j] = (!QUANT && use) ? RoundIntD(static_cast<double>(hz[j]) * hscale * cnt_factor) : 0;
-    pg += gz[j]; ph += hz[j]; pc += cz[j];
-    gz[j] = pg; hz[j] = ph; cz[j] = pc;     // in-lane inclusive prefix
-  }
-  long long bg = pg, bh = ph; int bc = pc;  // warp exclusive prefix of lane totals
+  const bool use = b < num_bin && b != nan_bin;
+  const long long gv = use ? g_in : 0, hv = use ? h_in : 0;
+  const int cv = (!QUANT && use) ? RoundIntD(static_cast<double>(hv) * hscale * cnt_factor) : 0;
+  // inclusive block scan
+  long long pg = gv, ph = hv; int pc = cv;
   #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const long long tg = __shfl_up_sync(0xffffffffu, bg, o);
-    const long long th = __shfl_up_sync(0xffffffffu, bh, o);
-    const int tc = __shfl_up_sync(0xffffffffu, bc, o);
-    if (lane >= o) { bg += tg; bh += th; bc += tc; }
+    const long long tg = __shfl_up_sync(0xffffffffu, pg, o);
+    const long long th = __shfl_up_sync(0xffffffffu, ph, o);
+    const int tc = __shfl_up_sync(0xffffffffu, pc, o);
+    if (lane >= o) { pg += tg; ph += th; pc += tc; }
   }
-  const long long Tg = __shfl_sync(0xffffffffu, bg, 31), Th = __shfl_sync(0xffffffffu, bh, 31);
-  const int Tc = __shfl_sync(0xffffffffu, bc, 31);
-  bg -= pg; bh -= ph; bc -= pc;
+  if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
+  __syncthreads();
+  long long Tg = 0, Th = 0; int Tc = 0;
+  #pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    if (w < warp) { pg += s_g[w]; ph += s_h[w]; pc += s_c[w]; }
+    Tg += s_g[w]; Th += s_h[w]; Tc += s_c[w];
+  }
   const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
   const double min_gain_shift = gain_shift + P.min_gain_to_split;
   bool splittable = false;
-  // ---- reverse scan: right = bins [b, top], threshold = b - 1, b in [1, top]
+  // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
   const int top = num_bin - 1 - (two_scans ? 1 : 0);
-  Cand best_r; best_r.gain = KMINSCORE; best_r.b = -1; best_r.sg = 0; best_r.sh = 0; best_r.cnt = 0;
-  #pragma unroll
-  for (int j = 7; j >= 0; --j) {
-    const int b = lane * 8 + j;
-    if (b < 1 || b > top) continue;
-    // suffix sum from b = total - inclusive prefix(b - 1)
-    const long long incl_g_prev = bg + (j > 0 ? gz[j - 1] : 0), incl_h_prev = bh + (j > 0 ? hz[j - 1] : 0);
-    const long long rgi = Tg - incl_g_prev, rhi = Th - incl_h_prev;
-    double gain; int rc;
+  Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
+  if (b >= 1 && b <= top) {
+    const long long rgi = Tg - (pg - gv), rhi = Th - (ph - hv);
+    double gain = 0.0; int rc; bool ok = true;
     if (QUANT) {
       rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
       const double srh = static_cast<double>(rhi) * hscale;
-      if (rc < P.min_data_in_leaf || srh < P.min_sum_hessian) continue;
       const int lc = num_data - rc;
-      if (lc < P.min_data_in_leaf) continue;
       const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
       const double slh = static_cast<double>(lhi) * hscale;
-      if (slh < P.min_sum_hessian) continue;
-      gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
+      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
     } else {
-      rc = Tc - (bc + (j > 0 ? cz[j - 1] : 0));
+      rc = Tc - (pc - cv);
       const double rh = KEPS + static_cast<double>(rhi) * hscale;
-      if (rc < P.min_data_in_leaf || rh < P.min_sum_hessian) continue;
       const int lc = num_data - rc;
-      if (lc < P.min_data_in_leaf) continue;
       const double lh = sum_hessian - rh;
-      if (lh < P.min_sum_hessian) continue;
-      const double rg = static_cast<double>(rgi) * gscale;
-      gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P);
+      ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
+      if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
     }
-    if (gain <= min_gain_shift) continue;
-    splittable = true;
-    if (gain > best_r.gain) { best_r.gain = gain; best_r.b = b; best_r.sg = rgi; best_r.sh = rhi; best_r.cnt = rc; }
+    if (ok && gain > min_gain_shift) { splittable = true; cr.gain = gain; cr.b = b; cr.sg = rgi; cr.sh = rhi; cr.cnt = rc; }
   }
-  best_r = WarpBestCand(best_r, true);
-  // ---- forward scan (NaN as missing): left = bins [0, b], threshold = b, b in [0, num_bin - 2]
-  Cand best_f; best_f.gain = KMINSCORE; best_f.b = -1; best_f.sg = 0; best_f.sh = 0; best_f.cnt = 0;
-  if (two_scans) {
-    #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int b = lane * 8 + j;
-      if (b > num_bin - 2) continue;
-      const long long lgi = bg + gz[j], lhi = bh + hz[j];
-      double gain; int lc;
-      if (QUANT) {
-        lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
-        const double slh = static_cast<double>(lhi) * hscale;
-        if (lc < P.min_data_in_leaf || slh < P.min_sum_hessian) continue;
-        const int rc = num_data - lc;
-        if (rc < P.min_data_in_leaf) continue;
-        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
-        const double srh = static_cast<double>(rhi) * hscale;
-        if (srh < P.min_sum_hessian) continue;
-        gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
-      } else {
-        lc = bc + cz[j];
-        const double lh = KEPS + static_cast<double>(lhi) * hscale;
-        if (lc < P.min_data_in_leaf || lh < P.min_sum_hessian) continue;
-        const int rc = num_data - lc;
-        if (rc < P.min_data_in_leaf) continue;
-        const double rh = sum_hessian - lh;
-        if (rh < P.min_sum_hessian) continue;
-        const double lg = static_cast<double>(lgi) * gscale;
-        gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P);
-      }
-      if (gain <= min_gain_shift) continue;
-      splittable = true;
-      if (gain > best_f.gain) { best_f.gain = gain; best_f.b = b; best_f.sg = lgi; best_f.sh = lhi; best_f.cnt = lc; }
+  // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
+  Cand cf; cf.gain = KMINSCORE; cf.b = -1; cf.sg = 0; cf.sh = 0; cf.cnt = 0;
+  if (two_scans && b <= num_bin - 2) {
+    const long long lgi = pg, lhi = ph;
+    double gain = 0.0; int lc; bool ok = true;
+    if (QUANT) {
+      lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+      const double slh = static_cast<double>(lhi) * hscale;
+      const int rc = num_data - lc;
+      const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+      const double srh = static_cast<double>(rhi) * hscale;
+      ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
+      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+    } else {
+      lc = pc;
+      const double lh = KEPS + static_cast<double>(lhi) * hscale;
+      const int rc = num_data - lc;
+      const double rh = sum_hessian - lh;
+      ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
+      if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
     }
-    best_f = WarpBestCand(best_f, false);
+    if (ok && gain > min_gain_shift) { splittable = true; cf.gain = gain; cf.b = b; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }
   }
-  splittable = __any_sync(0xffffffffu, splittable);
-  if (lane == 0) {
-    SplitDev s;
-    s.gain = KMINSCORE; s.feature = f; s.real_feature = fm.real_index; s.threshold = 0; s.default_left = 1;
-    s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
-    s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
-    s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
+  if (splittable) s_flag = 1;
+  const Cand best_r = BlockBestCand(cr, true, s_cand);
+  Cand best_f = cf;
+  if (two_scans) best_f = BlockBestCand(cf, false, s_cand);
+  __syncthreads();
+  if (b == 0) {
+    const bool any = s_flag != 0;
+    SplitDev s = EmptySplit(f, fm.real_index);
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;
-      if (!(splittable && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      if (!(any && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
       const bool reverse = pass == 0;
       if (QUANT) {
         const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
@@ -595,154 +651,44 @@ __device__ void WarpFindBest(const long long (&gz_in)[8], const long long (&hz_i
     }
     if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
     *out = s;
-    *splittable_out = splittable ? 1 : 0;
+    *splittable_out = any ? 1 : 0;
   }
 }
 
-// One warp per feature: stores the freshly built (smaller child's) histogram into its pool slot, derives the sibling
-// by subtraction from the parent's slot (K5), and searches both (K6).  root=1: only leaf 0, whose totals are the sum of
-// any feature's bins.
-template <bool QUANT>
-__global__ void __launch_bounds__(256) k_find(const long long* __restrict__ work, long long* __restrict__ pool,
-                                              const FeatureMetaDev* __restrict__ fmeta, LeafDev* __restrict__ leaves,
-                                              TreeCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
-                                              unsigned char* __restrict__ splittable, LearnerParams P, int root) {
-  if (ctrl->done) return;
-  if (!root && !ctrl->find) return;
-  const int F = P.num_features;
-  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (f >= F) return;
-  const int lane = threadIdx.x & 31;
-  const FeatureMetaDev fm = fmeta[f];
-  const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
-  const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
-  const long long* w = work + static_cast<size_t>(f) * kBins * 2 + lane * 16;
-  long long g[8], h[8];
-  #pragma unroll
-  for (int j = 0; j < 8; j += 1) {
-    const longlong2 v = *reinterpret_cast<const longlong2*>(w + 2 * j);
-    g[j] = v.x; h[j] = v.y;
-  }
-  if (root) {
-    long long tg = 0, th = 0;
-    #pragma unroll
-    for (int j = 0; j < 8; ++j) { tg += g[j]; th += h[j]; }
-    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
-    long long* dst = pool + static_cast<size_t>(leaves[0].hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
-    #pragma unroll
-    for (int j = 0; j < 8; ++j) *reinterpret_cast<longlong2*>(dst + 2 * j) = make_longlong2(g[j], h[j]);
-    const double sg = static_cast<double>(tg) * gscale, sh = static_cast<double>(th) * hscale;
-    if (f == 0 && lane == 0) { leaves[0].int_g = tg; leaves[0].int_h = th; leaves[0].sum_g = sg; leaves[0].sum_h = sh; }
-    WarpFindBest<QUANT>(g, h, fm, f, tg, th, sg, sh, leaves[0].global_count, P, gscale, hscale, feat_best + f, splittable + f);
-    return;
-  }
-  const int sm = ctrl->smaller, lg = ctrl->larger;
-  const int left = ctrl->cur_leaf;
-  const bool used = splittable[static_cast<size_t>(left) * F + f] != 0;     // the parent's flag (the left child reuses its id)
-  const LeafDev& Ls = leaves[sm];
-  const LeafDev& Ll = leaves[lg];
-  long long* ds = pool + static_cast<size_t>(Ls.hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
-  long long* dl = pool + static_cast<size_t>(Ll.hist_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
-  const long long* dp = pool + static_cast<size_t>(ctrl->parent_slot) * slot_stride + static_cast<size_t>(f) * kBins * 2 + lane * 16;
-  long long pgv[8], phv[8];
-  #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const longlong2 v = *reinterpret_cast<const longlong2*>(dp + 2 * j);
-    pgv[j] = v.x - g[j]; phv[j] = v.y - h[j];
-  }
-  #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    *reinterpret_cast<longlong2*>(ds + 2 * j) = make_longlong2(g[j], h[j]);
-    *reinterpret_cast<longlong2*>(dl + 2 * j) = make_longlong2(pgv[j], phv[j]);
-  }
-  SplitDev* outs = feat_best + f;
-  SplitDev* outl = feat_best + F + f;
-  unsigned char* spl_s = splittable + static_cast<size_t>(sm) * F + f;
-  unsigned char* spl_l = splittable + static_cast<size_t>(lg) * F + f;
-  if (!used) {
-    if (lane == 0) {
-      SplitDev s;
-      s.gain = KMINSCORE; s.feature = f; s.real_feature = fm.real_index; s.threshold = 0; s.default_left = 1;
-      s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
-      s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
-      s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
-      *outs = s; *outl = s; *spl_s = 0; *spl_l = 0;
-    }
-    return;
-  }
-  WarpFindBest<QUANT>(g, h, fm, f, Ls.int_g, Ls.int_h, Ls.sum_g, Ls.sum_h, Ls.global_count, P, gscale, hscale, outs, spl_s);
-  WarpFindBest<QUANT>(pgv, phv, fm, f, Ll.int_g, Ll.int_h, Ll.sum_g, Ll.sum_h, Ll.global_count, P, gscale, hscale, outl, spl_l);
-}
-
-// ------------------------------------------------------------------------------------------------ leaf selection + Tree::Split
-__device__ __forceinline__ bool SplitBetter(double ga, int fa, double gb, int fb) {
-  // upstream SplitInfo::operator>: larger gain; equal gain -> smaller real feature index (-1 = +inf)
-  const int a = fa < 0 ? 0x7fffffff : fa, b = fb < 0 ? 0x7fffffff : fb;
-  if (ga != gb) return ga > gb;
-  return a < b;
-}
-
-__global__ void __launch_bounds__(256) k_select(LeafDev* __restrict__ leaves, TreeCtrl* __restrict__ ctrl,
-                                                const SplitDev* __restrict__ feat_best, TreeArraysDev T,
-                                                const FeatureMetaDev* __restrict__ fmeta, LearnerParams P) {
-  if (ctrl->done) return;
-  __shared__ double s_gain[256];
-  __shared__ int s_feat[256], s_idx[256];
-  const int F = P.num_features;
-  // (1) reduce the per-feature results of the leaves searched by the previous k_find
-  const int pending = ctrl->pending;
-  for (int c = 0; c < pending; ++c) {
-    const SplitDev* fb = feat_best + static_cast<size_t>(c) * F;
-    double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int f = threadIdx.x; f < F; f += blockDim.x) {
-      const double g = fb[f].gain; const int rf = fb[f].real_feature;
-      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = f; }
-    }
-    s_gain[threadIdx.x] = bg; s_feat[threadIdx.x] = bf; s_idx[threadIdx.x] = bi;
-    __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-      if (threadIdx.x < o) {
-        const int t = threadIdx.x + o;
-        if (s_idx[t] >= 0 && (s_idx[threadIdx.x] < 0 || SplitBetter(s_gain[t], s_feat[t], s_gain[threadIdx.x], s_feat[threadIdx.x]))) {
-          s_gain[threadIdx.x] = s_gain[t]; s_feat[threadIdx.x] = s_feat[t]; s_idx[threadIdx.x] = s_idx[t];
-        }
-      }
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-      const int leaf = (pending == 1) ? 0 : (c == 0 ? ctrl->smaller : ctrl->larger);
-      leaves[leaf].best = fb[s_idx[0]];
-    }
-    __syncthreads();
-  }
-  // (2) leaf with the best split: (gain desc, feature asc, leaf asc)
+// Leaf selection + Tree::Split bookkeeping, run by one thread block (the last CTA of k_find to finish, so no extra launch):
+// picks the leaf with the best split (gain desc, feature asc, leaf asc); stops the tree when no gain is positive;
+// otherwise records the new internal node and publishes the split for the partition kernels.
+__device__ void SelectAndSplit(LeafDev* __restrict__ leaves, TreeCtrl* __restrict__ ctrl, TreeArraysDev T,
+                               const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P) {
+  __shared__ double s_gain[8];
+  __shared__ int s_feat[8], s_idx[8];
   const int nl = ctrl->num_leaves;
-  {
-    double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int l = threadIdx.x; l < nl; l += blockDim.x) {
-      const double g = leaves[l].best.gain; const int rf = leaves[l].best.real_feature;
-      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = l; }
-    }
-    s_gain[threadIdx.x] = bg; s_feat[threadIdx.x] = bf; s_idx[threadIdx.x] = bi;
-    __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-      if (threadIdx.x < o) {
-        const int t = threadIdx.x + o;
-        if (s_idx[t] >= 0) {
-          const bool better = s_idx[threadIdx.x] < 0 || SplitBetter(s_gain[t], s_feat[t], s_gain[threadIdx.x], s_feat[threadIdx.x]) ||
-                              (!SplitBetter(s_gain[threadIdx.x], s_feat[threadIdx.x], s_gain[t], s_feat[t]) && s_idx[t] < s_idx[threadIdx.x]);
-          if (better) { s_gain[threadIdx.x] = s_gain[t]; s_feat[threadIdx.x] = s_feat[t]; s_idx[threadIdx.x] = s_idx[t]; }
-        }
-      }
-      __syncthreads();
-    }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double bg = KMINSCORE; int bf = -1, bi = -1;
+  for (int l = threadIdx.x; l < nl; l += blockDim.x) {
+    const double g = leaves[l].best.gain; const int rf = leaves[l].best.real_feature;
+    if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = l; }   // ascending l: the earlier leaf keeps ties
   }
+  auto take = [&](double g, int rf, int i) {
+    if (i < 0) return;
+    if (bi < 0 || SplitBetter(g, rf, bg, bf) || (!SplitBetter(bg, bf, g, rf) && i < bi)) { bg = g; bf = rf; bi = i; }
+  };
+  for (int o = 16; o > 0; o >>= 1) {
+    const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+    const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+    const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+    take(g, rf, i);
+  }
+  __syncthreads();
+  if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
+  __syncthreads();
   if (threadIdx.x != 0) return;
+  bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
+  for (int w = 1; w < static_cast<int>(blockDim.x >> 5); ++w) take(s_gain[w], s_feat[w], s_idx[w]);
   ctrl->pending = 0;
-  const int best_leaf = s_idx[0];
+  const int best_leaf = bi;
   const SplitDev bs = leaves[best_leaf].best;
   if (!(bs.gain > 0.0) || nl >= P.num_leaves) { ctrl->done = 1; return; }
-  // (3) Tree::Split bookkeeping
   const int new_node = nl - 1, new_leaf = nl;
   const FeatureMetaDev fm = fmeta[bs.feature];
   const int parent = T.leaf_parent[best_leaf];
@@ -779,8 +725,129 @@ __global__ void __launch_bounds__(256) k_select(LeafDev* __restrict__ leaves, Tr
   ctrl->parent_slot = leaves[best_leaf].hist_slot;
 }
 
+// grid = (F, root ? 1 : 2): CTA (f, c) stores child c's histogram of feature f into its pool slot (c = 0: the freshly
+// built smaller child; c = 1: the larger child = parent - smaller, K5) and searches it (K6).  The last CTA of each child
+// reduces that child's per-feature results to the leaf's best split; the last CTA overall then selects the next leaf to
+// split (SelectAndSplit), so one launch covers K5, K6 and the leaf arg-max.
+template <bool QUANT>
+__global__ void __launch_bounds__(256) k_find(const long long* __restrict__ work, long long* __restrict__ pool,
+                                              const FeatureMetaDev* __restrict__ fmeta, LeafDev* __restrict__ leaves,
+                                              TreeCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
+                                              unsigned char* __restrict__ splittable, TreeArraysDev T, LearnerParams P, int root) {
+  if (ctrl->done) return;
+  __shared__ int s_last;
+  __shared__ double s_gain[8];
+  __shared__ int s_feat[8], s_idx[8];
+  if (!root && !ctrl->find) {
+    // BeforeFindBestSplit said no: nothing to search, but the next leaf still has to be chosen
+    if (blockIdx.x == 0 && blockIdx.y == 0) SelectAndSplit(leaves, ctrl, T, fmeta, P);
+    return;
+  }
+  const int F = P.num_features;
+  const int f = blockIdx.x, c = blockIdx.y, b = threadIdx.x;
+  const FeatureMetaDev fm = fmeta[f];
+  const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
+  const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
+  const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
+  const int leaf = root ? 0 : (c == 0 ? ctrl->smaller : ctrl->larger);
+  const LeafDev& Lf = leaves[leaf];
+  longlong2 v = *reinterpret_cast<const longlong2*>(work + off);
+  bool used = true;
+  if (!root) {
+    used = splittable[static_cast<size_t>(ctrl->cur_leaf) * F + f] != 0;   // the parent's flag (the left child reuses its id)
+    if (c == 1) {
+      const longlong2 p = *reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(ctrl->parent_slot) * slot_stride + off);
+      v.x = p.x - v.x; v.y = p.y - v.y;
+    }
+  }
+  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(Lf.hist_slot) * slot_stride + off) = v;
+  SplitDev* outp = feat_best + static_cast<size_t>(c) * F + f;
+  // the parent's flag row is read by both CTAs of feature f and rewritten by one of them: children flags go to a scratch
+  // row first and are copied when the child's reduction runs
+  unsigned char* spl = splittable + static_cast<size_t>(P.num_leaves + c) * F + f;
+  if (!used) {
+    if (b == 0) { *outp = EmptySplit(f, fm.real_index); *spl = 0; }
+  } else {
+    long long tg, th;
+    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, Lf.int_g, Lf.int_h, Lf.sum_g, Lf.sum_h, Lf.global_count, P, gscale, hscale,
+                         outp, spl, &tg, &th);
+    if (root && f == 0 && b == 0) {
+      leaves[0].int_g = tg; leaves[0].int_h = th;
+      leaves[0].sum_g = static_cast<double>(tg) * gscale; leaves[0].sum_h = static_cast<double>(th) * hscale;
+    }
+  }
+  // ---- last CTA of this child: per-feature results -> the leaf's best split
+  __threadfence();
+  __syncthreads();
+  if (b == 0) s_last = (atomicAdd(&ctrl->find_count[c], 1) == F - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  {
+    const SplitDev* fb = feat_best + static_cast<size_t>(c) * F;
+    const unsigned char* sp = splittable + static_cast<size_t>(P.num_leaves + c) * F;
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int j = b; j < F; j += blockDim.x) {
+      const double g = fb[j].gain; const int rf = fb[j].real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+    }
+    const int lane = b & 31, warp = b >> 5;
+    for (int o = 16; o > 0; o >>= 1) {
+      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
+    }
+    if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
+    __syncthreads();
+    if (b == 0) {
+      bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
+      for (int w = 1; w < 8; ++w)
+        if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
+      leaves[leaf].best = fb[bi];
+      ctrl->find_count[c] = 0;
+    }
+    // children inherit / refresh the per-feature splittable flags
+    unsigned char* dstrow = splittable + static_cast<size_t>(leaf) * F;
+    // The left child reuses the parent's leaf id, hence its flag row: that row may only be overwritten once every CTA of
+    // BOTH children has read it, i.e. by the child reduction that finishes last (below).
+    if (root) for (int j = b; j < F; j += blockDim.x) dstrow[j] = sp[j];
+    __threadfence();
+    __syncthreads();
+    if (b == 0) s_last = root ? 1 : (atomicAdd(&ctrl->find_children_done, 1) == 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (!root) {
+      // all CTAs of both children are done: now it is safe to overwrite the parent's flag row
+      for (int cc = 0; cc < 2; ++cc) {
+        const int lf2 = cc == 0 ? ctrl->smaller : ctrl->larger;
+        const unsigned char* src = splittable + static_cast<size_t>(P.num_leaves + cc) * F;
+        unsigned char* dst = splittable + static_cast<size_t>(lf2) * F;
+        for (int j = b; j < F; j += blockDim.x) dst[j] = src[j];
+      }
+      if (b == 0) ctrl->find_children_done = 0;
+    }
+    __threadfence();
+    __syncthreads();
+    SelectAndSplit(leaves, ctrl, T, fmeta, P);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ K7 stable partition
-// pass 1: left/right flag of every row of the leaf as one ballot word per warp + per-block left counts
+// A warp owns 32-row words of the leaf's index range: lanes are rows, one ballot gives the word's left/right flags.
+// pass 1 (count): flag word per 32 rows + per-block left counts.  pass 2 (scatter): block-local prefix over its words in
+// shared memory, then every warp writes its rows to the other index buffer with no further synchronisation; lefts and
+// rights each go to consecutive positions, so stores coalesce.  Order is preserved (the partition is stable).
+constexpr int kPartWordsPerIter = 2048;     // shared-memory prefix capacity (65536 rows) per block iteration
+
+__device__ __forceinline__ void PartChunk(int n, int* lo_w, int* hi_w) {
+  const int words = (n + 31) >> 5;
+  const int per = (words + gridDim.x - 1) / gridDim.x;
+  *lo_w = min(words, static_cast<int>(blockIdx.x) * per);
+  *hi_w = min(words, *lo_w + per);
+}
+
 __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __restrict__ cm, long long n_pad,
                                                              const int* __restrict__ idx0, const int* __restrict__ idx1,
                                                              const TreeCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
@@ -790,47 +857,58 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
   const int thr = ctrl->cur_threshold, nan_bin = ctrl->cur_nan_bin, dl = ctrl->cur_default_left;
   const uint8_t* col = cm + static_cast<size_t>(ctrl->cur_feature) * n_pad;
   const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
-  int chunk = (n + gridDim.x - 1) / gridDim.x;
-  chunk = (chunk + kPartThreads - 1) / kPartThreads * kPartThreads;
-  const int lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
+  int lo_w, hi_w;
+  PartChunk(n, &lo_w, &hi_w);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kPartThreads / 32;
   int cnt = 0;
-  for (int tile = lo; tile < hi; tile += kPartThreads) {
-    const int p = tile + threadIdx.x;
-    bool left = false;
-    if (p < hi) {
-      const int row = idx ? idx[begin + p] : begin + p;
-      const int bin = col[row];
-      left = (bin == nan_bin) ? (dl != 0) : (bin <= thr);
+  for (int w0 = lo_w + warp; w0 < hi_w; w0 += NW * 4) {
+    int rows[4];
+    #pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int w = w0 + u * NW;
+      const int p = w * 32 + lane;
+      rows[u] = (w < hi_w && p < n) ? (idx ? idx[begin + p] : begin + p) : -1;
     }
-    const unsigned int word = __ballot_sync(0xffffffffu, left);
-    if ((threadIdx.x & 31) == 0 && p < hi) flags[p >> 5] = word;
-    cnt += left;
+    int bins[4];
+    #pragma unroll
+    for (int u = 0; u < 4; ++u) bins[u] = rows[u] >= 0 ? col[rows[u]] : -1;
+    #pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int w = w0 + u * NW;
+      const bool left = rows[u] >= 0 && ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr));
+      const unsigned int word = __ballot_sync(0xffffffffu, left);
+      if (lane == 0 && w < hi_w) { flags[w] = word; cnt += __popc(word); }
+    }
   }
-  __shared__ int s_cnt[kPartThreads / 32];
-  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-  if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = cnt;
+  __shared__ int s_cnt[NW];
+  if (lane == 0) s_cnt[warp] = cnt;
   __syncthreads();
   if (threadIdx.x == 0) {
     int t = 0;
-    for (int i = 0; i < kPartThreads / 32; ++i) t += s_cnt[i];
+    for (int i = 0; i < NW; ++i) t += s_cnt[i];
     block_counts[blockIdx.x] = t;
   }
 }
 
-// pass 2: scatter into the other index buffer keeping order; block 0 also publishes the two children
 __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __restrict__ idx0r, const int* __restrict__ idx1r,
                                                                int* __restrict__ idx0w, int* __restrict__ idx1w,
                                                                TreeCtrl* __restrict__ ctrl, LeafDev* __restrict__ leaves,
                                                                const unsigned int* __restrict__ flags,
                                                                const int* __restrict__ block_counts, TreeArraysDev T,
-                                                               unsigned char* __restrict__ splittable, LearnerParams P) {
+                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
   if (ctrl->done) return;
+  // the histogram kernel of this split accumulates into `work` with atomics: clear it here (saves a memset node)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < work_elems; i += gridDim.x * blockDim.x) work[i] = 0;
   const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
   const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
   const int other = buf < 0 ? 0 : 1 - buf;
   int* dst = other == 0 ? idx0w : idx1w;
-  __shared__ int s_red[2][kPartThreads / 32];
-  __shared__ int s_wcnt[kPartThreads / 32];
+  constexpr int NW = kPartThreads / 32;
+  __shared__ int s_red[2][NW];
+  __shared__ int s_prefix[kPartWordsPerIter];
+  __shared__ int s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int before = 0, total = 0;
   for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
     const int c = block_counts[i];
@@ -838,30 +916,53 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
     if (i < blockIdx.x) before += c;
   }
   for (int o = 16; o > 0; o >>= 1) { before += __shfl_xor_sync(0xffffffffu, before, o); total += __shfl_xor_sync(0xffffffffu, total, o); }
-  if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = before; s_red[1][threadIdx.x >> 5] = total; }
+  if (lane == 0) { s_red[0][warp] = before; s_red[1][warp] = total; }
   __syncthreads();
   before = 0; total = 0;
-  for (int i = 0; i < kPartThreads / 32; ++i) { before += s_red[0][i]; total += s_red[1][i]; }
-  int chunk = (n + gridDim.x - 1) / gridDim.x;
-  chunk = (chunk + kPartThreads - 1) / kPartThreads * kPartThreads;
-  const int lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int running = before;
-  for (int tile = lo; tile < hi; tile += kPartThreads) {
-    const int p = tile + threadIdx.x;
-    const int wbase = tile + warp * 32;
-    const unsigned int word = (wbase < hi) ? flags[wbase >> 5] : 0u;
-    if (lane == 0) s_wcnt[warp] = __popc(word);
-    __syncthreads();
-    int wprefix = 0, tile_total = 0;
-    for (int i = 0; i < kPartThreads / 32; ++i) { const int c = s_wcnt[i]; tile_total += c; if (i < warp) wprefix += c; }
-    if (p < hi) {
-      const int row = idx ? idx[begin + p] : begin + p;
-      const int lefts_before = running + wprefix + __popc(word & ((1u << lane) - 1u));
-      if ((word >> lane) & 1u) dst[begin + lefts_before] = row;
-      else dst[begin + total + (p - lefts_before)] = row;
+  for (int i = 0; i < NW; ++i) { before += s_red[0][i]; total += s_red[1][i]; }
+  int lo_w, hi_w;
+  PartChunk(n, &lo_w, &hi_w);
+  if (threadIdx.x == 0) s_carry = before;
+  __syncthreads();
+  for (int base_w = lo_w; base_w < hi_w; base_w += kPartWordsPerIter) {
+    const int nw = min(kPartWordsPerIter, hi_w - base_w);
+    // exclusive prefix of popcounts over this iteration's words -> s_prefix (lefts before each word)
+    for (int t0 = 0; t0 < nw; t0 += kPartThreads) {
+      const int t = t0 + threadIdx.x;
+      int c = t < nw ? __popc(flags[base_w + t]) : 0;
+      int incl = c;
+      for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+      if (lane == 31) s_red[0][warp] = incl;
+      __syncthreads();
+      int wp = 0, tot = 0;
+      for (int i = 0; i < NW; ++i) { if (i < warp) wp += s_red[0][i]; tot += s_red[0][i]; }
+      if (t < nw) s_prefix[t] = s_carry + wp + incl - c;
+      __syncthreads();
+      if (threadIdx.x == 0) s_carry += tot;
+      __syncthreads();
     }
-    running += tile_total;
+    // scatter: one word per warp step, 4 words in flight
+    for (int w0 = warp; w0 < nw; w0 += NW * 4) {
+      int rows[4];
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int w = w0 + u * NW;
+        const int p = (base_w + w) * 32 + lane;
+        rows[u] = (w < nw && p < n) ? (idx ? idx[begin + p] : begin + p) : -1;
+      }
+      #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int w = w0 + u * NW;
+        if (w >= nw) continue;
+        const unsigned int word = flags[base_w + w];
+        const int p = (base_w + w) * 32 + lane;
+        if (rows[u] >= 0) {
+          const int lefts_before = s_prefix[w] + __popc(word & ((1u << lane) - 1u));
+          if ((word >> lane) & 1u) dst[begin + lefts_before] = rows[u];
+          else dst[begin + total + (p - lefts_before)] = rows[u];
+        }
+      }
+    }
     __syncthreads();
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -892,6 +993,7 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
     ctrl->smaller = smaller; ctrl->larger = larger; ctrl->find = find ? 1 : 0; ctrl->pending = find ? 2 : 0;
   }
 }
+
 
 // ------------------------------------------------------------------------------------------------ K8 score update
 // Leaf ranges partition [0, n); ranges are looked up by position.  score[row] += shrunk leaf value.
@@ -961,6 +1063,7 @@ __global__ void k_tree_init(LeafDev* leaves, TreeCtrl* ctrl, TreeArraysDev T, in
   if (i == 0) {
     ctrl->num_leaves = 1; ctrl->done = 0; ctrl->pending = 1; ctrl->find = 1; ctrl->smaller = 0; ctrl->larger = -1;
     ctrl->cur_leaf = 0; ctrl->new_leaf = 0;
+    ctrl->find_count[0] = 0; ctrl->find_count[1] = 0; ctrl->find_children_done = 0;
   }
 }
 

@@ -59,7 +59,7 @@ def higgs_shape(n, start=0, seed=20240601, f=28):
             else:
                 u = rng.random(CHUNK)
                 x[:, j] = np.where(u < 0.5, 0.0, np.where(u < 0.8, 1.0865, 2.1731))
-        z = 0.8 * x[:, 0] - 0.6 * x[:, 1] + 0.5 * np.sin(x[:, 2]) + 0.7 * (x[:, 3] > 1) + 0.3 * x[:, 4] * x[:, 8 % f] - 0.2
+        z = 0.8 * x[:, 0] - 0.6 * x[:, 1 % f] + 0.5 * np.sin(x[:, 2 % f]) + 0.7 * (x[:, 3 % f] > 1) + 0.3 * x[:, 4 % f] * x[:, 8 % f] - 0.2
         y = (rng.random(CHUNK) < 1.0 / (1.0 + np.exp(-z))).astype(np.float32)
         return x, y
     return _assemble(gen, n, start)
