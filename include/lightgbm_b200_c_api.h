@@ -142,6 +142,16 @@ int LGBM_B200_BoosterTimerStart(BoosterHandle handle);
 int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms);
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
 
+/* No counterpart in the reference.  Histogram (kernel K4, root-leaf case) for callers that may not allocate device memory:
+ * an executor plugin living inside an external memory pool or a fixed per-task GPU budget, or a loop that must not take the
+ * driver's allocation lock.  Its scratch (int64 accumulation area + descriptors, about 1 MB) is a static array in the
+ * library's device image: held by every GPU that loads the library until exit, shared by all calls (calls overlapping on one
+ * GPU race; this call clears what must start at zero), capacity num_features <= 256 (larger is refused with an error).  All
+ * pointers are device pointers; stream is a cudaStream_t or NULL.  The first call on a device resolves the array's address —
+ * make it before any stream capture.  Calls no cudaMalloc / cudaFree. */
+int LGBM_B200_RootHistogramNoAlloc(const uint8_t* d_rows, int32_t row_stride, const uint16_t* d_gh, int32_t num_rows,
+                                   int32_t num_features, int32_t num_grad_quant_bins, int64_t* d_out_hist, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

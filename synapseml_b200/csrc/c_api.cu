@@ -24,6 +24,11 @@ int Fail(const char* what) {
 }
 }  // namespace
 
+namespace lgb {
+// lets other translation units of the library report through LGBM_GetLastError()
+void SetLastErrorMessage(const char* m) { g_last_error = m; }
+}  // namespace lgb
+
 #define API_BEGIN() try {
 #define API_END()                                         \
   }                                                       \

@@ -15,17 +15,15 @@
 #include <cstdint>
 
 #include "booster.h"
+#include "hist_kernel.cuh"
 #include "softmath.cuh"
 
 namespace lgb {
 
 #define KEPS ((double)1e-15f)
 #define KMINSCORE (-__longlong_as_double(0x7ff0000000000000LL))
-constexpr int kBins = 256;
 constexpr int kFixBits = 19;                       // float mode: |fixed-point value| <= 2^19 per row
 constexpr int kFixRowsPerCopy = 4000;              // 4000 * 2^19 < 2^31
-constexpr int kHistThreads = 1024;
-constexpr int kHistMinRowsPerCta = 2048;
 constexpr int kPartBlocks = 592;                   // 4 x 148 SMs
 constexpr int kPartThreads = 256;
 
@@ -255,176 +253,6 @@ __global__ void k_quantize(const float* __restrict__ grad, const float* __restri
     }
   }
 }
-
-// ------------------------------------------------------------------------------------------------ K4 histogram
-// Shared-memory layout [array][bin][32 lanes]: in any one warp-wide atomic every lane hits its own bank, whatever the
-// bins are, so throughput does not depend on the bin distribution (measured on B200: 2.0-4.2 T updates/s against
-// 0.7-3.5 T/s for a [feature][bin] layout; profiles/r01_smem_atomics_microbench.log).  A lane covers BPL consecutive
-// feature bytes of one row; 32/R lanes cover one row record slice and R rows are handled per warp step, so each
-// feature has R private sub-histograms that are summed when the CTA flushes to the global int64 histogram.
-//   quantized: one RED.SHARED.ADD.U32 per (row, feature) on a packed (grad << 16) + hess word; a CTA flushes before any
-//              16-bit lane can overflow.
-//   float    : two RED.SHARED.ADD.U32 per (row, feature) on 32-bit fixed-point sums.
-// The four 32 KB arrays start at a 32 KB-aligned shared address, so the address of an update is
-// ((bins >> s) & 0x7f80) | lane_address — two ALU instructions per atomic.
-// Algorithmic bytes per row visit: F * 1 (bins) + 2 (quantized g,h) or 8 (float) + 4 (row index; 0 at the root).
-constexpr unsigned kHistArrayBytes = kBins * 32 * 4;       // 32 KB
-constexpr size_t kHistSmemBytes = 4 * kHistArrayBytes + kHistArrayBytes;   // + alignment slack
-
-// All of a lane's BPL updates for one row in one asm block: no per-update branch, array offsets as immediates.
-template <int BPL, bool FLT>
-__device__ __forceinline__ void HistUpdate(unsigned bins, unsigned lane_addr, unsigned pk, unsigned gx, unsigned hx) {
-  // byte k of `bins` -> byte offset bin * 128 inside array k
-  const unsigned a0 = ((bins << 7) & 0x7f80u) | lane_addr;
-  const unsigned a1 = ((bins >> 1) & 0x7f80u) | lane_addr;
-  if (FLT) {
-    asm volatile(
-        "red.shared.add.u32 [%0], %2;\n\t"
-        "red.shared.add.u32 [%0+32768], %3;\n\t"
-        "red.shared.add.u32 [%1+65536], %2;\n\t"
-        "red.shared.add.u32 [%1+98304], %3;" ::"r"(a0), "r"(a1), "r"(gx), "r"(hx) : "memory");
-  } else {
-    const unsigned a2 = ((bins >> 9) & 0x7f80u) | lane_addr;
-    const unsigned a3 = ((bins >> 17) & 0x7f80u) | lane_addr;
-    asm volatile(
-        "red.shared.add.u32 [%0], %4;\n\t"
-        "red.shared.add.u32 [%1+32768], %4;\n\t"
-        "red.shared.add.u32 [%2+65536], %4;\n\t"
-        "red.shared.add.u32 [%3+98304], %4;" ::"r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(pk) : "memory");
-  }
-}
-
-template <int R, int BPL, bool FLT, bool ROOT>
-__global__ void __launch_bounds__(kHistThreads, 1)
-k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-       const int* __restrict__ idx0, const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
-       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int rows_per_flush) {
-  extern __shared__ unsigned int hsm_raw[];
-  constexpr int LPR = 32 / R;                 // lanes per row
-  constexpr int FT = LPR * BPL;               // features per tile
-  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays (always 4)
-  static_assert(NARR == 4, "four 32 KB arrays");
-  if (ctrl->done) return;
-  if (!ROOT && !ctrl->find) return;
-  const LeafDev& lf = leaves[ROOT ? 0 : ctrl->smaller];
-  const int begin = lf.begin, count = lf.count, buf = lf.buf;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
-  }
-  int rows_per_cta = (count + gridDim.x - 1) / gridDim.x;
-  rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
-  const int lo = blockIdx.x * rows_per_cta;
-  const int hi = min(count, lo + rows_per_cta);
-  if (lo >= hi) return;
-  const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int q = lane % LPR, r = lane / LPR;
-  const int tile = blockIdx.y;
-  // 32 KB-aligned window inside the dynamic shared memory
-  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
-  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
-  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
-  const unsigned lane_addr = sbase + lane * 4;
-  // A lane works if its first feature byte is a real feature.  When F is not a multiple of BPL the last working lane also
-  // updates its zero-padded bytes (bin 0 of features >= F), which the flush ignores.
-  const bool kmask = (tile * FT + q * BPL) < F;
-  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + q * BPL;
-  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
-  __syncthreads();
-  constexpr int STEPS = 32 / R;
-  constexpr int U = 8;
-  for (int sub = lo; sub < hi; sub += rows_per_flush) {
-    const int sub_hi = min(hi, sub + rows_per_flush);
-    for (int p0 = sub + warp * 32; p0 < sub_hi; p0 += nwarps * 32) {
-      const int p = p0 + lane;
-      const bool v = p < sub_hi;
-      int row_l = -1;
-      if (v) row_l = ROOT ? begin + p : idx[begin + p];
-      unsigned pk_l = 0, gx_l = 0, hx_l = 0;
-      if (v) {
-        if (FLT) { const int2 t = ghfix[row_l]; gx_l = static_cast<unsigned>(t.x); hx_l = static_cast<unsigned>(t.y); }
-        else {
-          const unsigned w = gh16[row_l];
-          pk_l = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
-        }
-      }
-      if (p0 + 32 <= sub_hi) {
-        // full group of 32 rows: no per-row predicates
-        #pragma unroll 1
-        for (int s0 = 0; s0 < STEPS; s0 += U) {
-          unsigned bins[U];
-          #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int srcl = (s0 + u) * R + r;
-            const unsigned row = ROOT ? static_cast<unsigned>(begin + p0 + srcl) : static_cast<unsigned>(__shfl_sync(0xffffffffu, row_l, srcl));
-            bins[u] = 0;
-            if (kmask) {
-              const uint8_t* src = rmc + static_cast<size_t>(row) * rm_stride;
-              if (BPL == 4) bins[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
-              else bins[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
-            }
-          }
-          #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int srcl = (s0 + u) * R + r;
-            unsigned pk = 0, gx = 0, hx = 0;
-            if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
-            else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
-            if (kmask) HistUpdate<BPL, FLT>(bins[u], lane_addr, pk, gx, hx);
-          }
-        }
-      } else {
-        #pragma unroll 1
-        for (int s = 0; s < STEPS; ++s) {
-          const int srcl = s * R + r;
-          const int row = __shfl_sync(0xffffffffu, row_l, srcl);
-          unsigned pk = 0, gx = 0, hx = 0;
-          if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
-          else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
-          if (row >= 0 && kmask) {
-            const uint8_t* src = rmc + static_cast<size_t>(static_cast<unsigned>(row)) * rm_stride;
-            unsigned b;
-            if (BPL == 4) b = __ldg(reinterpret_cast<const unsigned int*>(src));
-            else b = __ldg(reinterpret_cast<const unsigned short*>(src));
-            HistUpdate<BPL, FLT>(b, lane_addr, pk, gx, hx);
-          }
-        }
-      }
-    }
-    __syncthreads();
-    // flush: sum the R sub-histograms of each (feature, bin) and add into the global int64 histogram
-    for (int i = threadIdx.x; i < BPL * kBins * LPR; i += blockDim.x) {
-      const int qq = i % LPR;
-      const int bin = (i / LPR) % kBins;
-      const int k = i / (LPR * kBins);
-      const int f = tile * FT + qq * BPL + k;
-      long long g = 0, h = 0;
-      #pragma unroll
-      for (int rr = 0; rr < R; ++rr) {
-        const int a = bin * 32 + rr * LPR + qq;
-        if (FLT) {
-          g += static_cast<int>(hsm[(2 * k) * (kBins * 32) + a]);
-          h += static_cast<int>(hsm[(2 * k + 1) * (kBins * 32) + a]);
-          hsm[(2 * k) * (kBins * 32) + a] = 0u;
-          hsm[(2 * k + 1) * (kBins * 32) + a] = 0u;
-        } else {
-          const int w = static_cast<int>(hsm[k * (kBins * 32) + a]);
-          h += w & 0xffff;
-          g += w >> 16;
-          hsm[k * (kBins * 32) + a] = 0u;
-        }
-      }
-      if (f < F && (g != 0 || h != 0)) {
-        unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
-        if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
-        if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
-      }
-    }
-    __syncthreads();
-  }
-}
-
 
 // ------------------------------------------------------------------------------------------------ K5 + K6 split search
 __device__ __forceinline__ double ThresholdL1D(double s, double l1) {
