@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
 
 #include "kernels.cuh"
 
@@ -17,6 +18,22 @@ constexpr int kNumSms = 148;
 template <typename K>
 void SetSmem(K kernel, size_t bytes) {
   LGB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+}
+// Launch with programmatic stream serialization: the kernel may become resident while its predecessor drains; it calls
+// PdlWait() before touching anything the predecessor wrote.
+template <typename... KArgs, typename... Args>
+void LaunchPdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  LGB_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
 }
 constexpr size_t kHistSmem = kHistSmemBytes;   // 4 x 32 KB arrays + 32 KB alignment slack, both modes
 }  // namespace
@@ -103,13 +120,39 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
 #undef SET_HIST_SMEM
   LGB_CUDA(cudaStreamSynchronize(stream_));
+  prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
 
 Booster::~Booster() {
   cudaSetDevice(device_);
+  try { ProfReport(); } catch (...) {}
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
   for (auto& e : hist_events_) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (timer_ev_[0]) { cudaEventDestroy(timer_ev_[0]); cudaEventDestroy(timer_ev_[1]); }
+}
+
+void Booster::ProfBegin(const char* name) {
+  if (!prof_) return;
+  ProfRec r{name, nullptr, nullptr};
+  LGB_CUDA(cudaEventCreate(&r.a)); LGB_CUDA(cudaEventCreate(&r.b));
+  LGB_CUDA(cudaEventRecord(r.a, stream_));
+  prof_recs_.push_back(r);
+}
+void Booster::ProfEnd() {
+  if (!prof_) return;
+  LGB_CUDA(cudaEventRecord(prof_recs_.back().b, stream_));
+}
+void Booster::ProfReport() {
+  if (!prof_ || prof_recs_.empty()) return;
+  LGB_CUDA(cudaStreamSynchronize(stream_));
+  std::map<std::string, std::pair<int, double>> agg;
+  for (auto& r : prof_recs_) {
+    float ms = 0; cudaEventElapsedTime(&ms, r.a, r.b);
+    agg[r.name].first++; agg[r.name].second += ms;
+    cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+  }
+  prof_recs_.clear();
+  for (auto& kv : agg) fprintf(stderr, "[prof] %-16s n=%6d total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second, 1e3 * kv.second.second / kv.second.first);
 }
 
 void Booster::Sync() const { LGB_CUDA(cudaStreamSynchronize(stream_)); }
@@ -278,8 +321,8 @@ void Booster::LaunchHist(bool root) {
                          d_leaves_.p, d_ctrl_.p, d_hist_work_.p, F_, rows_per_flush
 #define LAUNCH_HIST(RR, BPL, FLT)                                                                              \
   do {                                                                                                         \
-    if (root) k_hist<RR, BPL, FLT, true><<<grid, kHistThreads, kHistSmem, stream_>>>(LAUNCH_HIST_ARGS);        \
-    else k_hist<RR, BPL, FLT, false><<<grid, kHistThreads, kHistSmem, stream_>>>(LAUNCH_HIST_ARGS);            \
+    if (root) LaunchPdl(k_hist<RR, BPL, FLT, true>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);   \
+    else LaunchPdl(k_hist<RR, BPL, FLT, false>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);       \
   } while (0)
   if (!flt) {
     if (R == 4) LAUNCH_HIST(4, 4, false); else if (R == 2) LAUNCH_HIST(2, 4, false); else LAUNCH_HIST(1, 4, false);
@@ -297,11 +340,11 @@ void Booster::LaunchHist(bool root) {
 void Booster::LaunchFind(bool root) {
   dim3 grid(F_, root ? 1 : 2);
   if (lp_.quantized)
-    k_find<true><<<grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p,
-                                            d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+    LaunchPdl(k_find<true>, grid, dim3(256), 0, stream_, d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p,
+              d_feat_best_.p, d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
   else
-    k_find<false><<<grid, 256, 0, stream_>>>(d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p, d_feat_best_.p,
-                                             d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+    LaunchPdl(k_find<false>, grid, dim3(256), 0, stream_, d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p,
+              d_feat_best_.p, d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
   ++launches_;
 }
 
@@ -314,17 +357,21 @@ void Booster::TrainTree(HostTree* out) {
   k_tree_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
-  LaunchHist(true);
-  LaunchFind(true);
+  ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
+  ProfBegin("find"); LaunchFind(true); ProfEnd();
   for (int split = 0; split < L - 1; ++split) {
-    k_part_count<<<kPartBlocks, kPartThreads, 0, stream_>>>(ds_->d_cm.p, ds_->n_pad, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
-    k_part_scatter<<<kPartBlocks, kPartThreads, 0, stream_>>>(d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_leaves_.p,
-                                                              d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p,
-                                                              static_cast<int>(d_hist_work_.n), lp_);
+    ProfBegin("part_count");
+    LaunchPdl(k_part_count, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+              d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
+    ProfEnd();
+    ProfBegin("part_scatter");
+    LaunchPdl(k_part_scatter, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p,
+              d_ctrl_.p, d_leaves_.p, d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p, static_cast<int>(d_hist_work_.n), lp_);
+    ProfEnd();
     launches_ += 2;
     if (split < L - 2) {
-      LaunchHist(false);
-      LaunchFind(false);
+      ProfBegin("hist"); LaunchHist(false); ProfEnd();
+      ProfBegin("find"); LaunchFind(false); ProfEnd();
     }
   }
   LGB_CUDA(cudaGetLastError());
@@ -410,14 +457,14 @@ bool Booster::UpdateOneIter() {
   tree.num_leaves = 1;
   tree.leaf_value.assign(1, 0.0);
   if (need_train_ && F_ > 0) {
-    ComputeGradients();
-    PrepareGradients();
+    ProfBegin("gradients"); ComputeGradients(); ProfEnd();
+    ProfBegin("quantize"); PrepareGradients(); ProfEnd();
     TrainTree(&tree);
   }
   bool should_continue = false;
   if (tree.num_leaves > 1) {
     should_continue = true;
-    UpdateScores();
+    ProfBegin("score_update"); UpdateScores(); ProfEnd();
     tree.Shrinkage(cfg_.learning_rate);
     if (std::fabs(init_score) > kEps) tree.AddBias(init_score);
   } else if (models_.empty()) {

@@ -141,6 +141,13 @@ class Booster {
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;
   cudaEvent_t timer_ev_[2] = {nullptr, nullptr};
+  // per-kernel-type timing with CUDA events (LGB_B200_PROFILE=1): development aid, breaks launch overlap
+  bool prof_ = false;
+  struct ProfRec { const char* name; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof_recs_;
+  void ProfBegin(const char* name);
+  void ProfEnd();
+  void ProfReport();
 
   void InitObjective();
   double BoostFromScoreLocalSums(double* suml, double* sumw) const;

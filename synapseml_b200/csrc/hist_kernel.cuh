@@ -13,6 +13,13 @@ constexpr int kBins = 256;
 constexpr int kHistThreads = 1024;
 constexpr int kHistMinRowsPerCta = 2048;
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still draining.  PdlLaunchDependents() lets the successor's CTAs become resident;
+// PdlWait() blocks until the predecessor grid has completed and its writes are visible.  Everything before PdlWait() must
+// not touch memory the predecessor writes.
+__device__ __forceinline__ void PdlLaunchDependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void PdlWait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------------------------------------ K4 histogram
 // Shared-memory layout [array][bin][32 lanes]: in any one warp-wide atomic every lane hits its own bank, whatever the
 // bins are, so throughput does not depend on the bin distribution (measured on B200: 2.0-4.2 T updates/s against
@@ -61,6 +68,25 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
   constexpr int FT = LPR * BPL;               // features per tile
   constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays (always 4)
   static_assert(NARR == 4, "four 32 KB arrays");
+  PdlLaunchDependents();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int q = lane % LPR, r = lane / LPR;
+  const int tile = blockIdx.y;
+  // 32 KB-aligned window inside the dynamic shared memory
+  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
+  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
+  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
+  const unsigned lane_addr = sbase + lane * 4;
+  // A lane works if its first feature byte is a real feature (when F is not a multiple of BPL the last working lane also
+  // updates its zero-padded bytes, bin 0 of features >= F, which the flush ignores).  In the hot loop the other lanes are
+  // not predicated off: they read the tile's first feature bytes instead and update their own columns, which the flush
+  // ignores as well — no branch, no hot address.
+  const bool kmask = (tile * FT + q * BPL) < F;
+  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + (kmask ? q : 0) * BPL;
+  asm volatile("" : "+l"(rmc));      // keep the pointer in registers (no re-derivation from the parameter bank per load)
+  // clearing the shared histograms overlaps the predecessor kernel's tail
+  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
+  PdlWait();
   if (ctrl->done) return;
   if (!ROOT && !ctrl->find) return;
   const LeafDev& lf = leaves[ROOT ? 0 : ctrl->smaller];
@@ -75,77 +101,106 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
   const int hi = min(count, lo + rows_per_cta);
   if (lo >= hi) return;
   const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int q = lane % LPR, r = lane / LPR;
-  const int tile = blockIdx.y;
-  // 32 KB-aligned window inside the dynamic shared memory
-  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
-  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
-  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
-  const unsigned lane_addr = sbase + lane * 4;
-  // A lane works if its first feature byte is a real feature.  When F is not a multiple of BPL the last working lane also
-  // updates its zero-padded bytes (bin 0 of features >= F), which the flush ignores.
-  const bool kmask = (tile * FT + q * BPL) < F;
-  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + q * BPL;
-  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
   __syncthreads();
   constexpr int STEPS = 32 / R;
   constexpr int U = 8;
   for (int sub = lo; sub < hi; sub += rows_per_flush) {
     const int sub_hi = min(hi, sub + rows_per_flush);
-    for (int p0 = sub + warp * 32; p0 < sub_hi; p0 += nwarps * 32) {
-      const int p = p0 + lane;
+    // ---- this warp's full 32-row groups, software-pipelined: while one unit's updates issue, the next unit's bins and the
+    //      next group's row ids / gradients are already in flight (the kernel is latency-bound otherwise)
+    const int first = sub + warp * 32;
+    const int gstride = nwarps * 32;
+    const int ng = (first + 32 <= sub_hi) ? (sub_hi - 32 - first) / gstride + 1 : 0;
+    constexpr int NU = STEPS / U;
+    auto load_row = [&](int p0) -> int { return ROOT ? begin + p0 + lane : idx[begin + p0 + lane]; };
+    auto load_gh = [&](int row, unsigned& pk, unsigned& gx, unsigned& hx) {
+      if (FLT) { const int2 t = ghfix[row]; gx = static_cast<unsigned>(t.x); hx = static_cast<unsigned>(t.y); }
+      else {
+        const unsigned w = gh16[row];
+        pk = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+      }
+    };
+    auto load_bins = [&](int row_l, int p0, int unit, unsigned (&bb)[U]) {
+      if (ROOT) {
+        // rows of a group are consecutive: one pointer per group, constant offsets per load
+        const uint8_t* gp = rmc + static_cast<size_t>(static_cast<unsigned>(begin + p0 + r)) * rm_stride;
+        #pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint8_t* src = gp + static_cast<size_t>((unit * U + u) * R) * rm_stride;
+          if (BPL == 4) bb[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
+          else bb[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
+        }
+      } else {
+        #pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const unsigned row = static_cast<unsigned>(__shfl_sync(0xffffffffu, row_l, (unit * U + u) * R + r));
+          const uint8_t* src = rmc + static_cast<size_t>(row) * rm_stride;
+          if (BPL == 4) bb[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
+          else bb[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
+        }
+      }
+    };
+    if (ng > 0) {
+      int row_cur = load_row(first);
+      int row_nxt = ng > 1 ? load_row(first + gstride) : 0;
+      unsigned pk_cur = 0, gx_cur = 0, hx_cur = 0;
+      load_gh(row_cur, pk_cur, gx_cur, hx_cur);
+      unsigned b_cur[U];
+      load_bins(row_cur, first, 0, b_cur);
+      #pragma unroll 1
+      for (int j = 0; j < ng; ++j) {
+        const int p0 = first + j * gstride;
+        int row_nn = 0;
+        unsigned pk_nxt = 0, gx_nxt = 0, hx_nxt = 0;
+        #pragma unroll
+        for (int unit = 0; unit < NU; ++unit) {
+          unsigned b_nxt[U];
+          if (unit + 1 < NU) {
+            load_bins(row_cur, p0, unit + 1, b_nxt);
+          } else if (j + 1 < ng) {
+            load_gh(row_nxt, pk_nxt, gx_nxt, hx_nxt);
+            load_bins(row_nxt, p0 + gstride, 0, b_nxt);
+            if (j + 2 < ng) row_nn = load_row(p0 + 2 * gstride);
+          } else {
+            #pragma unroll
+            for (int u = 0; u < U; ++u) b_nxt[u] = 0;
+          }
+          #pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int srcl = (unit * U + u) * R + r;
+            unsigned pk = 0, gx = 0, hx = 0;
+            if (FLT) { gx = __shfl_sync(0xffffffffu, gx_cur, srcl); hx = __shfl_sync(0xffffffffu, hx_cur, srcl); }
+            else pk = __shfl_sync(0xffffffffu, pk_cur, srcl);
+            HistUpdate<BPL, FLT>(b_cur[u], lane_addr, pk, gx, hx);
+          }
+          #pragma unroll
+          for (int u = 0; u < U; ++u) b_cur[u] = b_nxt[u];
+        }
+        row_cur = row_nxt; row_nxt = row_nn; pk_cur = pk_nxt; gx_cur = gx_nxt; hx_cur = hx_nxt;
+      }
+    }
+    // ---- the warp's partial last group, if any: per-row predicates
+    const int ptail = first + ng * gstride;
+    if (ptail < sub_hi) {
+      const int p = ptail + lane;
       const bool v = p < sub_hi;
       int row_l = -1;
       if (v) row_l = ROOT ? begin + p : idx[begin + p];
       unsigned pk_l = 0, gx_l = 0, hx_l = 0;
-      if (v) {
-        if (FLT) { const int2 t = ghfix[row_l]; gx_l = static_cast<unsigned>(t.x); hx_l = static_cast<unsigned>(t.y); }
-        else {
-          const unsigned w = gh16[row_l];
-          pk_l = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
-        }
-      }
-      if (p0 + 32 <= sub_hi) {
-        // full group of 32 rows: no per-row predicates
-        #pragma unroll 1
-        for (int s0 = 0; s0 < STEPS; s0 += U) {
-          unsigned bins[U];
-          #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int srcl = (s0 + u) * R + r;
-            const unsigned row = ROOT ? static_cast<unsigned>(begin + p0 + srcl) : static_cast<unsigned>(__shfl_sync(0xffffffffu, row_l, srcl));
-            bins[u] = 0;
-            if (kmask) {
-              const uint8_t* src = rmc + static_cast<size_t>(row) * rm_stride;
-              if (BPL == 4) bins[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
-              else bins[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
-            }
-          }
-          #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int srcl = (s0 + u) * R + r;
-            unsigned pk = 0, gx = 0, hx = 0;
-            if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
-            else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
-            if (kmask) HistUpdate<BPL, FLT>(bins[u], lane_addr, pk, gx, hx);
-          }
-        }
-      } else {
-        #pragma unroll 1
-        for (int s = 0; s < STEPS; ++s) {
-          const int srcl = s * R + r;
-          const int row = __shfl_sync(0xffffffffu, row_l, srcl);
-          unsigned pk = 0, gx = 0, hx = 0;
-          if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
-          else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
-          if (row >= 0 && kmask) {
-            const uint8_t* src = rmc + static_cast<size_t>(static_cast<unsigned>(row)) * rm_stride;
-            unsigned b;
-            if (BPL == 4) b = __ldg(reinterpret_cast<const unsigned int*>(src));
-            else b = __ldg(reinterpret_cast<const unsigned short*>(src));
-            HistUpdate<BPL, FLT>(b, lane_addr, pk, gx, hx);
-          }
+      if (v) load_gh(row_l, pk_l, gx_l, hx_l);
+      #pragma unroll 1
+      for (int s = 0; s < STEPS; ++s) {
+        const int srcl = s * R + r;
+        const int row = __shfl_sync(0xffffffffu, row_l, srcl);
+        unsigned pk = 0, gx = 0, hx = 0;
+        if (FLT) { gx = __shfl_sync(0xffffffffu, gx_l, srcl); hx = __shfl_sync(0xffffffffu, hx_l, srcl); }
+        else pk = __shfl_sync(0xffffffffu, pk_l, srcl);
+        if (row >= 0 && kmask) {
+          const uint8_t* src = rmc + static_cast<size_t>(static_cast<unsigned>(row)) * rm_stride;
+          unsigned bb;
+          if (BPL == 4) bb = __ldg(reinterpret_cast<const unsigned int*>(src));
+          else bb = __ldg(reinterpret_cast<const unsigned short*>(src));
+          HistUpdate<BPL, FLT>(bb, lane_addr, pk, gx, hx);
         }
       }
     }

@@ -562,6 +562,8 @@ __global__ void __launch_bounds__(256) k_find(const long long* __restrict__ work
                                               const FeatureMetaDev* __restrict__ fmeta, LeafDev* __restrict__ leaves,
                                               TreeCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
                                               unsigned char* __restrict__ splittable, TreeArraysDev T, LearnerParams P, int root) {
+  PdlLaunchDependents();
+  PdlWait();
   if (ctrl->done) return;
   __shared__ int s_last;
   __shared__ double s_gain[8];
@@ -680,6 +682,8 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
                                                              const int* __restrict__ idx0, const int* __restrict__ idx1,
                                                              const TreeCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
                                                              int* __restrict__ block_counts) {
+  PdlLaunchDependents();
+  PdlWait();
   if (ctrl->done) return;
   const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
   const int thr = ctrl->cur_threshold, nan_bin = ctrl->cur_nan_bin, dl = ctrl->cur_default_left;
@@ -725,6 +729,8 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
                                                                const unsigned int* __restrict__ flags,
                                                                const int* __restrict__ block_counts, TreeArraysDev T,
                                                                long long* __restrict__ work, int work_elems, LearnerParams P) {
+  PdlLaunchDependents();
+  PdlWait();
   if (ctrl->done) return;
   // the histogram kernel of this split accumulates into `work` with atomics: clear it here (saves a memset node)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < work_elems; i += gridDim.x * blockDim.x) work[i] = 0;
