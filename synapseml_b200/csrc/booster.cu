@@ -6,6 +6,7 @@
 #include <map>
 
 #include "kernels.cuh"
+#include "tree_kernel.cuh"
 
 namespace lgb {
 
@@ -58,6 +59,9 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   device_ = train->device;
   LGB_CUDA(cudaSetDevice(device_));
   LGB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  // Histogram passes over non-root leaves gather one 32-byte row record per visited row: ask L2 not to over-fetch 64 bytes
+  // per miss (the default granularity), which doubles the DRAM traffic of sparse gathers.  A hint; failure is harmless.
+  if (getenv("LGB_B200_L2_FETCH_64") == nullptr) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 32);
   net_ = Network::Get();
   net_->EnsureComm(device_);
   n_ = train->num_data;
@@ -88,7 +92,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   if (train->has_init_score) LGB_CUDA(cudaMemcpy(d_score_.p, train->d_init_score.p, sizeof(double) * n_, cudaMemcpyDeviceToDevice));
   d_grad_.Alloc(n_); d_hess_.Alloc(n_);
   if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
-  d_idx_[0].Alloc(n_); d_idx_[1].Alloc(n_);
+  idx_es_ = lp_.quantized ? 2 : 4;      // ints per index entry: {row, g|h} or {row, g, h, -}
+  d_idx_[0].Alloc(n_ * idx_es_); d_idx_[1].Alloc(n_ * idx_es_);
   d_flags_.Alloc(n_ / 32 + 2 * kPartThreads);
   d_part_counts_.AllocZero(kPartBlocks);
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
@@ -119,6 +124,21 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
 #undef SET_HIST_SMEM
+#define SET_TREE_SMEM(RR, BPL, FLT) SetSmem(k_tree<RR, BPL, FLT>, kHistSmem)
+  SET_TREE_SMEM(4, 4, false); SET_TREE_SMEM(2, 4, false); SET_TREE_SMEM(1, 4, false);
+  SET_TREE_SMEM(4, 2, true); SET_TREE_SMEM(2, 2, true); SET_TREE_SMEM(1, 2, true);
+#undef SET_TREE_SMEM
+  {
+    // the persistent tree kernel needs every CTA resident at once (cooperative launch): one CTA per SM
+    int dev_sms = 0, coop = 0;
+    LGB_CUDA(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, device_));
+    LGB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_));
+    int per_sm = 0;
+    LGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tree<4, 4, false>, kTreeThreads, kHistSmem));
+    tree_grid_ = (coop && per_sm >= 1) ? dev_sms : 0;
+    const char* env = getenv("LGB_B200_MULTI_KERNEL");
+    if (env != nullptr && env[0] == '1') tree_grid_ = 0;
+  }
   LGB_CUDA(cudaStreamSynchronize(stream_));
   prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
@@ -152,6 +172,10 @@ void Booster::ProfReport() {
     cudaEventDestroy(r.a); cudaEventDestroy(r.b);
   }
   prof_recs_.clear();
+  if (prof_phase_[0] > 0) {
+    static const char* kNames[6] = {"tree(all)", "hist", "find", "select", "part_count", "part_scatter"};
+    for (int k = 0; k < 6; ++k) fprintf(stderr, "[prof] tree phase %-14s %6.1f %% of tree cycles\n", kNames[k], 100.0 * prof_phase_[k] / prof_phase_[0]);
+  }
   for (auto& kv : agg) fprintf(stderr, "[prof] %-16s n=%6d total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second, 1e3 * kv.second.second / kv.second.first);
 }
 
@@ -348,12 +372,59 @@ void Booster::LaunchFind(bool root) {
   ++launches_;
 }
 
+// Single-GPU learner: the whole tree in one cooperative launch (tree_kernel.cuh).
+bool Booster::TrainTreePersistent() {
+  const BinLayout& lay = ds_->layout;
+  const int R = lay.rows_per_step;
+  const bool flt = !lp_.quantized;
+  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
+  const int tiles = CeilDiv(F_, ft);
+  if (tree_grid_ <= 0 || net_->active() || tiles > tree_grid_) return false;
+  TreeKernelArgs a;
+  a.rm = ds_->d_rm.p; a.rm_stride = static_cast<unsigned>(lay.rm_stride); a.cm = ds_->d_cm.p; a.n_pad = ds_->n_pad;
+  a.fmeta = ds_->d_fmeta.p; a.gh16 = d_gh16_.p; a.ghfix = d_ghfix_.p; a.idx0 = d_idx_[0].p; a.idx1 = d_idx_[1].p; a.es = idx_es_;
+  a.flags = d_flags_.p; a.part_counts = d_part_counts_.p; a.work = d_hist_work_.p; a.pool = d_hist_pool_.p;
+  a.leaves = d_leaves_.p; a.ctrl = d_ctrl_.p; a.feat_best = d_feat_best_.p; a.splittable = d_splittable_.p;
+  a.T = tree_dev_; a.P = lp_; a.F = F_; a.work_elems = static_cast<int>(d_hist_work_.n);
+  if (flt) {
+    a.rows_per_flush = kFixRowsPerCopy * R;
+  } else {
+    const int qb = cfg_.num_grad_quant_bins;
+    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
+    a.rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
+  }
+  a.n_local = static_cast<int>(n_); a.n_global = static_cast<int>(n_global_);
+  void* args[] = {&a};
+  const void* fn = nullptr;
+  if (!flt) fn = R == 4 ? (const void*)k_tree<4, 4, false> : R == 2 ? (const void*)k_tree<2, 4, false> : (const void*)k_tree<1, 4, false>;
+  else fn = R == 4 ? (const void*)k_tree<4, 2, true> : R == 2 ? (const void*)k_tree<2, 2, true> : (const void*)k_tree<1, 2, true>;
+  ProfBegin("tree");
+  if (time_hist_) {      // one event pair around the whole tree; the histogram share comes from the kernel's own cycle counters
+    if (hist_events_.empty()) {
+      cudaEvent_t e0, e1;
+      LGB_CUDA(cudaEventCreate(&e0)); LGB_CUDA(cudaEventCreate(&e1));
+      hist_events_.emplace_back(e0, e1);
+    }
+    LGB_CUDA(cudaEventRecord(hist_events_[0].first, stream_));
+  }
+  LGB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(tree_grid_), dim3(kTreeThreads), args, kHistSmem, stream_));
+  if (time_hist_) { LGB_CUDA(cudaEventRecord(hist_events_[0].second, stream_)); tree_event_pending_ = true; }
+  ProfEnd();
+  ++launches_;
+  return true;
+}
+
+// Multi-kernel path (data-parallel learner, or when the persistent kernel cannot be used).
 // One tree = a fixed sequence of launches with device-resident control flow (no host round trip until the tree is read back):
 //   root: hist -> find(+select);  per split: part_count -> part_scatter -> hist(smaller child) -> find(+select)
 void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
   hist_events_used_ = 0;
+  if (TrainTreePersistent()) {
+    FetchTree(out);
+    return;
+  }
   k_tree_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
@@ -362,11 +433,11 @@ void Booster::TrainTree(HostTree* out) {
   for (int split = 0; split < L - 1; ++split) {
     ProfBegin("part_count");
     LaunchPdl(k_part_count, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-              d_idx_[0].p, d_idx_[1].p, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
+              d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
     ProfEnd();
     ProfBegin("part_scatter");
     LaunchPdl(k_part_scatter, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p,
-              d_ctrl_.p, d_leaves_.p, d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p, static_cast<int>(d_hist_work_.n), lp_);
+              idx_es_, d_gh16_.p, d_ghfix_.p, d_ctrl_.p, d_leaves_.p, d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p, static_cast<int>(d_hist_work_.n), lp_);
     ProfEnd();
     launches_ += 2;
     if (split < L - 2) {
@@ -386,7 +457,25 @@ void Booster::FetchTree(HostTree* t) {
   Sync();
   last_rows_visited_ += hc.hist_rows;
   hist_launches_ += hc.hist_launches;
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, 2 * sizeof(long long), stream_));
+  if (tree_event_pending_) {
+    float ms = 0;
+    LGB_CUDA(cudaEventElapsedTime(&ms, hist_events_[0].first, hist_events_[0].second));
+    if (hc.tree_cycles > 0) last_hist_ms_ += ms * static_cast<double>(hc.hist_cycles) / static_cast<double>(hc.tree_cycles);
+    tree_event_pending_ = false;
+  }
+  if (prof_ && hc.tree_cycles > 0 && iter_ == 10) {
+    fprintf(stderr, "[dbg] empty grid.sync = %lld cycles\n", hc.dbg[191]);
+    for (int i = 0; i < 30; ++i)
+      fprintf(stderr, "[dbg] split %2d smaller_rows=%8lld hist=%7lld find=%6lld select=%6lld count=%6lld scatter=%6lld cycles\n", i,
+              hc.dbg[i * 6 + 0], hc.dbg[i * 6 + 1], hc.dbg[i * 6 + 2], hc.dbg[i * 6 + 3], hc.dbg[i * 6 + 4], hc.dbg[i * 6 + 5]);
+  }
+  if (prof_ && hc.tree_cycles > 0) {
+    static const char* kNames[6] = {"init", "hist", "find", "select", "part_count", "part_scatter"};
+    for (int k = 1; k < 6; ++k) prof_phase_[k] += static_cast<double>(hc.phase_cycles[k]);
+    prof_phase_[0] += static_cast<double>(hc.tree_cycles);
+    (void)kNames;
+  }
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, 12 * sizeof(long long), stream_));
   const int nl = hc.num_leaves;
   t->num_leaves = nl;
   t->shrinkage = 1.0;
@@ -417,7 +506,7 @@ void Booster::UpdateScores() {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
   k_sort_leaves<<<1, 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, d_sorted_leaf_.p, L);
-  k_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, d_leaves_.p, d_ctrl_.p,
+  k_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, idx_es_, d_leaves_.p, d_ctrl_.p,
                                                                              d_sorted_leaf_.p, L, tree_dev_.leaf_value, cfg_.learning_rate, n);
   LGB_CUDA(cudaGetLastError());
   launches_ += 2;

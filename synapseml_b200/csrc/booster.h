@@ -50,6 +50,9 @@ struct TreeCtrl {
   double inv_grad_scale, inv_hess_scale;
   long long hist_rows;              // rows visited by histogram launches since the host last cleared it
   long long hist_launches;          // histogram launches that did work since the host last cleared it
+  long long phase_cycles[8];          // persistent kernel, CTA 0: init, hist, find, select, count, scatter
+  long long hist_cycles, tree_cycles;
+  long long dbg[192];                 // development aid: per split (rows, hist cycles, count cycles, scatter cycles, find, select)   // persistent kernel: SM cycles CTA 0 spent in histogram phases / in the whole tree
 };
 
 struct TreeArraysDev {
@@ -138,11 +141,15 @@ class Booster {
   int64_t last_rows_visited_ = 0, hist_launches_ = 0;
   double last_hist_ms_ = 0;
   int launches_ = 0;
+  bool tree_event_pending_ = false;
+  int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
+  int tree_grid_ = 0;               // CTAs of the persistent tree kernel (0: not available)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;
   cudaEvent_t timer_ev_[2] = {nullptr, nullptr};
   // per-kernel-type timing with CUDA events (LGB_B200_PROFILE=1): development aid, breaks launch overlap
   bool prof_ = false;
+  double prof_phase_[6] = {0, 0, 0, 0, 0, 0};
   struct ProfRec { const char* name; cudaEvent_t a, b; };
   std::vector<ProfRec> prof_recs_;
   void ProfBegin(const char* name);
@@ -156,6 +163,7 @@ class Booster {
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
   void LaunchFind(bool root);
+  bool TrainTreePersistent();
   void FetchTree(HostTree* out);
   void UpdateScores();
   ModelHeader MakeHeader() const;

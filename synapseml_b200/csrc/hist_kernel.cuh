@@ -58,50 +58,18 @@ __device__ __forceinline__ void HistUpdate(unsigned bins, unsigned lane_addr, un
   }
 }
 
+// Accumulates rows [lo, hi) of a leaf (positions into its index range; ROOT: positions are row ids) into the CTA's shared
+// histograms and flushes them into the global int64 histogram `work` (every rows_per_flush rows and at the end).  The shared
+// arrays must be zero on entry and are zero again on return.  Shared by k_hist and the persistent tree kernel.
 template <int R, int BPL, bool FLT, bool ROOT>
-__global__ void __launch_bounds__(kHistThreads, 1)
-k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-       const int* __restrict__ idx0, const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
-       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int rows_per_flush) {
-  extern __shared__ unsigned int hsm_raw[];
-  constexpr int LPR = 32 / R;                 // lanes per row
-  constexpr int FT = LPR * BPL;               // features per tile
-  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays (always 4)
-  static_assert(NARR == 4, "four 32 KB arrays");
-  PdlLaunchDependents();
+__device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride, const uint16_t* __restrict__ gh16,
+                                         const int2* __restrict__ ghfix, const int* idx, int begin, int lo, int hi,
+                                         unsigned lane_addr, unsigned int* hsm, long long* work, int F, int tile,
+                                         int rows_per_flush, bool kmask) {
+  constexpr int LPR = 32 / R;
+  constexpr int FT = LPR * BPL;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int q = lane % LPR, r = lane / LPR;
-  const int tile = blockIdx.y;
-  // 32 KB-aligned window inside the dynamic shared memory
-  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
-  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
-  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
-  const unsigned lane_addr = sbase + lane * 4;
-  // A lane works if its first feature byte is a real feature (when F is not a multiple of BPL the last working lane also
-  // updates its zero-padded bytes, bin 0 of features >= F, which the flush ignores).  In the hot loop the other lanes are
-  // not predicated off: they read the tile's first feature bytes instead and update their own columns, which the flush
-  // ignores as well — no branch, no hot address.
-  const bool kmask = (tile * FT + q * BPL) < F;
-  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + (kmask ? q : 0) * BPL;
-  asm volatile("" : "+l"(rmc));      // keep the pointer in registers (no re-derivation from the parameter bank per load)
-  // clearing the shared histograms overlaps the predecessor kernel's tail
-  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
-  PdlWait();
-  if (ctrl->done) return;
-  if (!ROOT && !ctrl->find) return;
-  const LeafDev& lf = leaves[ROOT ? 0 : ctrl->smaller];
-  const int begin = lf.begin, count = lf.count, buf = lf.buf;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
-  }
-  int rows_per_cta = (count + gridDim.x - 1) / gridDim.x;
-  rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
-  const int lo = blockIdx.x * rows_per_cta;
-  const int hi = min(count, lo + rows_per_cta);
-  if (lo >= hi) return;
-  const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
-  __syncthreads();
+  const int r = lane / LPR;
   constexpr int STEPS = 32 / R;
   constexpr int U = 8;
   for (int sub = lo; sub < hi; sub += rows_per_flush) {
@@ -112,12 +80,22 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
     const int gstride = nwarps * 32;
     const int ng = (first + 32 <= sub_hi) ? (sub_hi - 32 - first) / gstride + 1 : 0;
     constexpr int NU = STEPS / U;
-    auto load_row = [&](int p0) -> int { return ROOT ? begin + p0 + lane : idx[begin + p0 + lane]; };
-    auto load_gh = [&](int row, unsigned& pk, unsigned& gx, unsigned& hx) {
-      if (FLT) { const int2 t = ghfix[row]; gx = static_cast<unsigned>(t.x); hx = static_cast<unsigned>(t.y); }
-      else {
-        const unsigned w = gh16[row];
-        pk = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+    // one index entry per row of a non-root leaf: {row, packed g|h} (quantized) or {row, g, h, -} (float); the root reads the
+    // per-row gradient arrays directly (rows are consecutive)
+    auto load_entry = [&](int p, int& row, unsigned& pk, unsigned& gx, unsigned& hx) {
+      if (ROOT) {
+        row = begin + p;
+        if (FLT) { const int2 t = ghfix[row]; gx = static_cast<unsigned>(t.x); hx = static_cast<unsigned>(t.y); }
+        else {
+          const unsigned w = gh16[row];
+          pk = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+        }
+      } else if (FLT) {
+        const int4 e = reinterpret_cast<const int4*>(idx)[begin + p];
+        row = e.x; gx = static_cast<unsigned>(e.y); hx = static_cast<unsigned>(e.z);
+      } else {
+        const int2 e = reinterpret_cast<const int2*>(idx)[begin + p];
+        row = e.x; pk = static_cast<unsigned>(e.y);
       }
     };
     auto load_bins = [&](int row_l, int p0, int unit, unsigned (&bb)[U]) {
@@ -141,26 +119,25 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
       }
     };
     if (ng > 0) {
-      int row_cur = load_row(first);
-      int row_nxt = ng > 1 ? load_row(first + gstride) : 0;
-      unsigned pk_cur = 0, gx_cur = 0, hx_cur = 0;
-      load_gh(row_cur, pk_cur, gx_cur, hx_cur);
+      int row_cur = 0, row_nxt = 0;
+      unsigned pk_cur = 0, gx_cur = 0, hx_cur = 0, pk_nxt = 0, gx_nxt = 0, hx_nxt = 0;
+      load_entry(first + lane, row_cur, pk_cur, gx_cur, hx_cur);
+      if (ng > 1) load_entry(first + gstride + lane, row_nxt, pk_nxt, gx_nxt, hx_nxt);
       unsigned b_cur[U];
       load_bins(row_cur, first, 0, b_cur);
       #pragma unroll 1
       for (int j = 0; j < ng; ++j) {
         const int p0 = first + j * gstride;
         int row_nn = 0;
-        unsigned pk_nxt = 0, gx_nxt = 0, hx_nxt = 0;
+        unsigned pk_nn = 0, gx_nn = 0, hx_nn = 0;
         #pragma unroll
         for (int unit = 0; unit < NU; ++unit) {
           unsigned b_nxt[U];
           if (unit + 1 < NU) {
             load_bins(row_cur, p0, unit + 1, b_nxt);
           } else if (j + 1 < ng) {
-            load_gh(row_nxt, pk_nxt, gx_nxt, hx_nxt);
             load_bins(row_nxt, p0 + gstride, 0, b_nxt);
-            if (j + 2 < ng) row_nn = load_row(p0 + 2 * gstride);
+            if (j + 2 < ng) load_entry(p0 + 2 * gstride + lane, row_nn, pk_nn, gx_nn, hx_nn);
           } else {
             #pragma unroll
             for (int u = 0; u < U; ++u) b_nxt[u] = 0;
@@ -176,7 +153,9 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
           #pragma unroll
           for (int u = 0; u < U; ++u) b_cur[u] = b_nxt[u];
         }
-        row_cur = row_nxt; row_nxt = row_nn; pk_cur = pk_nxt; gx_cur = gx_nxt; hx_cur = hx_nxt;
+        row_cur = row_nxt; row_nxt = row_nn;
+        pk_cur = pk_nxt; gx_cur = gx_nxt; hx_cur = hx_nxt;
+        pk_nxt = pk_nn; gx_nxt = gx_nn; hx_nxt = hx_nn;
       }
     }
     // ---- the warp's partial last group, if any: per-row predicates
@@ -185,9 +164,8 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
       const int p = ptail + lane;
       const bool v = p < sub_hi;
       int row_l = -1;
-      if (v) row_l = ROOT ? begin + p : idx[begin + p];
       unsigned pk_l = 0, gx_l = 0, hx_l = 0;
-      if (v) load_gh(row_l, pk_l, gx_l, hx_l);
+      if (v) load_entry(p, row_l, pk_l, gx_l, hx_l);
       #pragma unroll 1
       for (int s = 0; s < STEPS; ++s) {
         const int srcl = s * R + r;
@@ -237,5 +215,51 @@ k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __res
   }
 }
 
+template <int R, int BPL, bool FLT, bool ROOT>
+__global__ void __launch_bounds__(kHistThreads, 1)
+k_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+       const int* __restrict__ idx0, const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
+       TreeCtrl* __restrict__ ctrl, long long* __restrict__ work, int F, int rows_per_flush) {
+  extern __shared__ unsigned int hsm_raw[];
+  constexpr int LPR = 32 / R;                 // lanes per row
+  constexpr int FT = LPR * BPL;               // features per tile
+  constexpr int NARR = FLT ? 2 * BPL : BPL;   // 32 KB arrays (always 4)
+  static_assert(NARR == 4, "four 32 KB arrays");
+  PdlLaunchDependents();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int q = lane % LPR, r = lane / LPR;
+  const int tile = blockIdx.y;
+  // 32 KB-aligned window inside the dynamic shared memory
+  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
+  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
+  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
+  const unsigned lane_addr = sbase + lane * 4;
+  // A lane works if its first feature byte is a real feature (when F is not a multiple of BPL the last working lane also
+  // updates its zero-padded bytes, bin 0 of features >= F, which the flush ignores).  In the hot loop the other lanes are
+  // not predicated off: they read the tile's first feature bytes instead and update their own columns, which the flush
+  // ignores as well — no branch, no hot address.
+  const bool kmask = (tile * FT + q * BPL) < F;
+  const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + (kmask ? q : 0) * BPL;
+  asm volatile("" : "+l"(rmc));      // keep the pointer in registers (no re-derivation from the parameter bank per load)
+  // clearing the shared histograms overlaps the predecessor kernel's tail
+  for (int i = threadIdx.x; i < NARR * kBins * 32; i += blockDim.x) hsm[i] = 0u;
+  PdlWait();
+  if (ctrl->done) return;
+  if (!ROOT && !ctrl->find) return;
+  const LeafDev& lf = leaves[ROOT ? 0 : ctrl->smaller];
+  const int begin = lf.begin, count = lf.count, buf = lf.buf;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
+    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
+  }
+  int rows_per_cta = (count + gridDim.x - 1) / gridDim.x;
+  rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
+  const int lo = blockIdx.x * rows_per_cta;
+  const int hi = min(count, lo + rows_per_cta);
+  if (lo >= hi) return;
+  const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
+  __syncthreads();
+  HistRows<R, BPL, FLT, ROOT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm, work, F, tile, rows_per_flush, kmask);
+}
 
 }  // namespace lgb

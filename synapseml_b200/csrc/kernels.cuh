@@ -294,12 +294,18 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
   return s;
 }
 
+// Split search runs on 256-thread sub-blocks (one per feature x child); a CTA may hold more than one of them (the persistent
+// tree kernel runs two), so they synchronise on named barriers instead of __syncthreads().
+constexpr int kFindThreads = 256;
+constexpr int kMaxFindSubs = 2;
+__device__ __forceinline__ void SubSync(int sub) { asm volatile("bar.sync %0, %1;" ::"r"(sub + 1), "n"(kFindThreads) : "memory"); }
+
 struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right: reverse, left: forward)
 
 // block-wide argmax of candidates; ties on gain go to the larger (reverse scan) or smaller (forward scan) bin, which is
 // what a sequential scan with a strict '>' keeps
-__device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand* s_c /*[8]*/) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand* s_c /*[8]*/, int sub) {
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x & (kFindThreads - 1)) >> 5;
   auto better = [&](const Cand& t, const Cand& cur) {
     return (t.gain > cur.gain) || (t.gain == cur.gain && t.b >= 0 && (cur.b < 0 || (prefer_larger_b ? t.b > cur.b : t.b < cur.b)));
   };
@@ -312,9 +318,9 @@ __device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand
     t.cnt = __shfl_xor_sync(0xffffffffu, c.cnt, o);
     if (better(t, c)) c = t;
   }
-  __syncthreads();
+  SubSync(sub);
   if (lane == 0) s_c[warp] = c;
-  __syncthreads();
+  SubSync(sub);
   Cand r = s_c[0];
   #pragma unroll
   for (int w = 1; w < 8; ++w) if (better(s_c[w], r)) r = s_c[w];
@@ -329,12 +335,14 @@ template <bool QUANT>
 __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
                               long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
                               double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
-                              long long* out_tot_g, long long* out_tot_h) {
-  __shared__ long long s_g[8], s_h[8];
-  __shared__ int s_c[8];
-  __shared__ Cand s_cand[8];
-  __shared__ int s_flag;
-  const int b = threadIdx.x, lane = b & 31, warp = b >> 5;
+                              long long* out_tot_g, long long* out_tot_h, int sub) {
+  __shared__ long long s_g_all[kMaxFindSubs][8], s_h_all[kMaxFindSubs][8];
+  __shared__ int s_c_all[kMaxFindSubs][8];
+  __shared__ Cand s_cand_all[kMaxFindSubs][8];
+  __shared__ int s_flag_all[kMaxFindSubs];
+  long long* s_g = s_g_all[sub]; long long* s_h = s_h_all[sub]; int* s_c = s_c_all[sub]; Cand* s_cand = s_cand_all[sub];
+  int& s_flag = s_flag_all[sub];
+  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
   const int num_bin = fm.num_bin;
   const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
   const int nan_bin = two_scans ? num_bin - 1 : -1;
@@ -344,13 +352,13 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     long long tg = g_in, th = h_in;
     for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
     if (lane == 0) { s_g[warp] = tg; s_h[warp] = th; }
-    __syncthreads();
+    SubSync(sub);
     tot_g = 0; tot_h = 0;
     #pragma unroll
     for (int w = 0; w < 8; ++w) { tot_g += s_g[w]; tot_h += s_h[w]; }
     leaf_sum_g = static_cast<double>(tot_g) * gscale;
     leaf_sum_h = static_cast<double>(tot_h) * hscale;
-    __syncthreads();
+    SubSync(sub);
   }
   *out_tot_g = tot_g; *out_tot_h = tot_h;
   double sum_gradient, sum_hessian, cnt_factor;
@@ -376,7 +384,7 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     if (lane >= o) { pg += tg; ph += th; pc += tc; }
   }
   if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
-  __syncthreads();
+  SubSync(sub);
   long long Tg = 0, Th = 0; int Tc = 0;
   #pragma unroll
   for (int w = 0; w < 8; ++w) {
@@ -434,10 +442,10 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     if (ok && gain > min_gain_shift) { splittable = true; cf.gain = gain; cf.b = b; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }
   }
   if (splittable) s_flag = 1;
-  const Cand best_r = BlockBestCand(cr, true, s_cand);
+  const Cand best_r = BlockBestCand(cr, true, s_cand, sub);
   Cand best_f = cf;
-  if (two_scans) best_f = BlockBestCand(cf, false, s_cand);
-  __syncthreads();
+  if (two_scans) best_f = BlockBestCand(cf, false, s_cand, sub);
+  SubSync(sub);
   if (b == 0) {
     const bool any = s_flag != 0;
     SplitDev s = EmptySplit(f, fm.real_index);
@@ -488,8 +496,8 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
 // otherwise records the new internal node and publishes the split for the partition kernels.
 __device__ void SelectAndSplit(LeafDev* __restrict__ leaves, TreeCtrl* __restrict__ ctrl, TreeArraysDev T,
                                const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P) {
-  __shared__ double s_gain[8];
-  __shared__ int s_feat[8], s_idx[8];
+  __shared__ double s_gain[32];
+  __shared__ int s_feat[32], s_idx[32];
   const int nl = ctrl->num_leaves;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double bg = KMINSCORE; int bf = -1, bi = -1;
@@ -600,7 +608,7 @@ __global__ void __launch_bounds__(256) k_find(const long long* __restrict__ work
   } else {
     long long tg, th;
     BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, Lf.int_g, Lf.int_h, Lf.sum_g, Lf.sum_h, Lf.global_count, P, gscale, hscale,
-                         outp, spl, &tg, &th);
+                         outp, spl, &tg, &th, 0);
     if (root && f == 0 && b == 0) {
       leaves[0].int_g = tg; leaves[0].int_h = th;
       leaves[0].sum_g = static_cast<double>(tg) * gscale; leaves[0].sum_h = static_cast<double>(th) * hscale;
@@ -678,13 +686,9 @@ __device__ __forceinline__ void PartChunk(int n, int* lo_w, int* hi_w) {
   *hi_w = min(words, *lo_w + per);
 }
 
-__global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __restrict__ cm, long long n_pad,
-                                                             const int* __restrict__ idx0, const int* __restrict__ idx1,
-                                                             const TreeCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
-                                                             int* __restrict__ block_counts) {
-  PdlLaunchDependents();
-  PdlWait();
-  if (ctrl->done) return;
+// Body shared by the k_part_count kernel and the persistent tree kernel (any block size that is a multiple of 32, <= 1024).
+__device__ __forceinline__ void PartCountBody(const uint8_t* __restrict__ cm, long long n_pad, const int* idx0, const int* idx1,
+                                              int es, const TreeCtrl* ctrl, unsigned int* flags, int* block_counts) {
   const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
   const int thr = ctrl->cur_threshold, nan_bin = ctrl->cur_nan_bin, dl = ctrl->cur_default_left;
   const uint8_t* col = cm + static_cast<size_t>(ctrl->cur_feature) * n_pad;
@@ -692,7 +696,7 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
   int lo_w, hi_w;
   PartChunk(n, &lo_w, &hi_w);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NW = kPartThreads / 32;
+  const int NW = blockDim.x >> 5;
   int cnt = 0;
   for (int w0 = lo_w + warp; w0 < hi_w; w0 += NW * 4) {
     int rows[4];
@@ -700,7 +704,7 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
     for (int u = 0; u < 4; ++u) {
       const int w = w0 + u * NW;
       const int p = w * 32 + lane;
-      rows[u] = (w < hi_w && p < n) ? (idx ? idx[begin + p] : begin + p) : -1;
+      rows[u] = (w < hi_w && p < n) ? (idx ? idx[static_cast<size_t>(begin + p) * es] : begin + p) : -1;
     }
     int bins[4];
     #pragma unroll
@@ -713,7 +717,8 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
       if (lane == 0 && w < hi_w) { flags[w] = word; cnt += __popc(word); }
     }
   }
-  __shared__ int s_cnt[NW];
+  __shared__ int s_cnt[32];
+  __syncthreads();
   if (lane == 0) s_cnt[warp] = cnt;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -723,23 +728,32 @@ __global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __re
   }
 }
 
-__global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __restrict__ idx0r, const int* __restrict__ idx1r,
-                                                               int* __restrict__ idx0w, int* __restrict__ idx1w,
-                                                               TreeCtrl* __restrict__ ctrl, LeafDev* __restrict__ leaves,
-                                                               const unsigned int* __restrict__ flags,
-                                                               const int* __restrict__ block_counts, TreeArraysDev T,
-                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
+__global__ void __launch_bounds__(kPartThreads) k_part_count(const uint8_t* __restrict__ cm, long long n_pad,
+                                                             const int* __restrict__ idx0, const int* __restrict__ idx1, int es,
+                                                             const TreeCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
+                                                             int* __restrict__ block_counts) {
   PdlLaunchDependents();
   PdlWait();
   if (ctrl->done) return;
+  PartCountBody(cm, n_pad, idx0, idx1, es, ctrl, flags, block_counts);
+}
+
+// Index entries carry the row's gradient pair along with the row id, so a histogram pass over a non-root leaf reads them
+// densely instead of gathering 2-8 bytes per row from a sparse set of sectors:
+//   quantized (es = 2 ints): {row, (g << 16) + h}        float mode (es = 4 ints): {row, g_fixed, h_fixed, 0}
+__device__ __forceinline__ void PartScatterBody(const int* idx0r, const int* idx1r, int* idx0w, int* idx1w, int es,
+                                                const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix, TreeCtrl* ctrl,
+                                                LeafDev* leaves, const unsigned int* flags, const int* block_counts,
+                                                TreeArraysDev T, long long* work, int work_elems, const LearnerParams& P) {
   // the histogram kernel of this split accumulates into `work` with atomics: clear it here (saves a memset node)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < work_elems; i += gridDim.x * blockDim.x) work[i] = 0;
   const int n = ctrl->src_count, begin = ctrl->src_begin, buf = ctrl->src_buf;
   const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
   const int other = buf < 0 ? 0 : 1 - buf;
   int* dst = other == 0 ? idx0w : idx1w;
-  constexpr int NW = kPartThreads / 32;
-  __shared__ int s_red[2][NW];
+  const int NW = blockDim.x >> 5;
+  const int NT = blockDim.x;
+  __shared__ int s_red[2][32];
   __shared__ int s_prefix[kPartWordsPerIter];
   __shared__ int s_carry;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -761,7 +775,7 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
   for (int base_w = lo_w; base_w < hi_w; base_w += kPartWordsPerIter) {
     const int nw = min(kPartWordsPerIter, hi_w - base_w);
     // exclusive prefix of popcounts over this iteration's words -> s_prefix (lefts before each word)
-    for (int t0 = 0; t0 < nw; t0 += kPartThreads) {
+    for (int t0 = 0; t0 < nw; t0 += NT) {
       const int t = t0 + threadIdx.x;
       int c = t < nw ? __popc(flags[base_w + t]) : 0;
       int incl = c;
@@ -777,12 +791,25 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
     }
     // scatter: one word per warp step, 4 words in flight
     for (int w0 = warp; w0 < nw; w0 += NW * 4) {
-      int rows[4];
+      int4 ent[4];
       #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int w = w0 + u * NW;
         const int p = (base_w + w) * 32 + lane;
-        rows[u] = (w < nw && p < n) ? (idx ? idx[begin + p] : begin + p) : -1;
+        ent[u] = make_int4(-1, 0, 0, 0);
+        if (w < nw && p < n) {
+          if (idx) {
+            if (es == 2) { const int2 e = reinterpret_cast<const int2*>(idx)[begin + p]; ent[u].x = e.x; ent[u].y = e.y; }
+            else ent[u] = reinterpret_cast<const int4*>(idx)[begin + p];
+          } else {           // the root: rows are 0..n-1, gradients come from the per-row arrays
+            const int row = begin + p;
+            ent[u].x = row;
+            if (es == 2) {
+              const unsigned int g = gh16[row];
+              ent[u].y = static_cast<int>((static_cast<unsigned>(static_cast<int>(static_cast<signed char>(g >> 8))) << 16) + (g & 0xffu));
+            } else { const int2 g = ghfix[row]; ent[u].y = g.x; ent[u].z = g.y; }
+          }
+        }
       }
       #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -790,10 +817,11 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
         if (w >= nw) continue;
         const unsigned int word = flags[base_w + w];
         const int p = (base_w + w) * 32 + lane;
-        if (rows[u] >= 0) {
+        if (ent[u].x >= 0) {
           const int lefts_before = s_prefix[w] + __popc(word & ((1u << lane) - 1u));
-          if ((word >> lane) & 1u) dst[begin + lefts_before] = rows[u];
-          else dst[begin + total + (p - lefts_before)] = rows[u];
+          const int pos = ((word >> lane) & 1u) ? begin + lefts_before : begin + total + (p - lefts_before);
+          if (es == 2) reinterpret_cast<int2*>(dst)[pos] = make_int2(ent[u].x, ent[u].y);
+          else reinterpret_cast<int4*>(dst)[pos] = ent[u];
         }
       }
     }
@@ -829,6 +857,19 @@ __global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __rest
 }
 
 
+__global__ void __launch_bounds__(kPartThreads) k_part_scatter(const int* __restrict__ idx0r, const int* __restrict__ idx1r,
+                                                               int* __restrict__ idx0w, int* __restrict__ idx1w, int es,
+                                                               const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+                                                               TreeCtrl* __restrict__ ctrl, LeafDev* __restrict__ leaves,
+                                                               const unsigned int* __restrict__ flags,
+                                                               const int* __restrict__ block_counts, TreeArraysDev T,
+                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
+  PdlLaunchDependents();
+  PdlWait();
+  if (ctrl->done) return;
+  PartScatterBody(idx0r, idx1r, idx0w, idx1w, es, gh16, ghfix, ctrl, leaves, flags, block_counts, T, work, work_elems, P);
+}
+
 // ------------------------------------------------------------------------------------------------ K8 score update
 // Leaf ranges partition [0, n); ranges are looked up by position.  score[row] += shrunk leaf value.
 __global__ void __launch_bounds__(256) k_sort_leaves(const LeafDev* __restrict__ leaves, const TreeCtrl* __restrict__ ctrl,
@@ -848,7 +889,7 @@ __global__ void __launch_bounds__(256) k_sort_leaves(const LeafDev* __restrict__
 }
 
 __global__ void __launch_bounds__(256) k_score_update(double* __restrict__ score, const int* __restrict__ idx0,
-                                                      const int* __restrict__ idx1, const LeafDev* __restrict__ leaves,
+                                                      const int* __restrict__ idx1, int es, const LeafDev* __restrict__ leaves,
                                                       const TreeCtrl* __restrict__ ctrl, const int* __restrict__ sorted, int L,
                                                       const double* __restrict__ leaf_value, double lr, int n) {
   __shared__ int s_begin[1024], s_leaf[1024];
@@ -871,7 +912,7 @@ __global__ void __launch_bounds__(256) k_score_update(double* __restrict__ score
       const int mid = (lo + hi + 1) >> 1;
       if (s_begin[mid] <= p) lo = mid; else hi = mid - 1;
     }
-    const int row = (s_buf[lo] == 0 ? idx0 : idx1)[p];
+    const int row = (s_buf[lo] == 0 ? idx0 : idx1)[static_cast<size_t>(p) * es];
     score[row] += s_val[lo];
   }
 }
