@@ -201,8 +201,9 @@ def main():
     ms_total = float(t.item())
     value = N * args.steps / (ms_total * 1e-3)
     launches = sb["kernel_launches"] - sa["kernel_launches"]
-    # second pass of the same length with the histogram kernel timed (CUDA events on the launching stream; in the persistent
-    # tree kernel: the kernel's own cycle counters scaled by the event time of the launch): roofline numbers only
+    growth = {k: (sb[k] - sa[k]) / args.steps for k in ("growth_rounds", "growth_expansions", "growth_splits")}
+    # second pass of the same length with every histogram launch bracketed by CUDA events on the launching stream (the events
+    # break the programmatic overlap between launches, so this pass is a little slower): roofline numbers only
     booster.set_hist_timing(True)
     s0 = booster.stats()
     booster.timer_start()
@@ -231,7 +232,7 @@ def main():
                 "algorithmic_bytes": "per row visit: 28 bin bytes + 2 (int8 g,h) + 4 row index (0 at the root); + F*256*16 output per launch",
                 "hist_ms_per_step": hist_ms / args.steps, "hist_share_of_step": hist_ms / ms_timed_pass,
                 "rows_visited_per_step": hist_rows / args.steps, "hist_launches_per_step": hist_launches / args.steps,
-                "avg_launch_us": hist_ms * 1e3 / max(hist_launches, 1),
+                "avg_us_per_leaf_histogram": hist_ms * 1e3 / max(hist_launches, 1),
                 "root_launch": {"ms": root_ms.value, "achieved": root_gbs, "frac": root_gbs / peak}}
     booster.free_native_memory()
     dataset.close()
@@ -269,7 +270,8 @@ def main():
                       "l2": "inputs larger than L2 (binned matrix %d MB per GPU + 2x%d MB index buffers vs 126 MB L2)" % (n_local * 32 >> 20, n_local * 4 >> 20),
                       "timing": "CUDA events on the library's launching stream, max over ranks; wall %.1f ms" % wall_ms,
                       "ingest_seconds_untimed": ingest_s},
-           "clocks": clocks_summary(clk_path, local_rank), "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+           "clocks": clocks_summary(clk_path, local_rank), "e2e": e2e, "gpu_launches": int(launches), "growth_per_step": growth,
+           "roofline": roofline,
            "cpu_baseline": cb}
     print(json.dumps(out), flush=True)
     if world > 1:

@@ -5,8 +5,8 @@
 #include <cstring>
 #include <map>
 
+#include "batch_tree.cuh"
 #include "kernels.cuh"
-#include "tree_kernel.cuh"
 
 namespace lgb {
 
@@ -94,16 +94,29 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
   idx_es_ = lp_.quantized ? 2 : 4;      // ints per index entry: {row, g|h} or {row, g, h, -}
   d_idx_[0].Alloc(n_ * idx_es_); d_idx_[1].Alloc(n_ * idx_es_);
-  d_flags_.Alloc(n_ / 32 + 2 * kPartThreads);
-  d_part_counts_.AllocZero(kPartBlocks);
+  // batched best-first learner (batch_tree.cuh): up to max_batch_ leaves are expanded per round; spec_budget_ bounds the
+  // expansions that are not guaranteed to be committed
+  {
+    const char* env = getenv("LGB_B200_MAX_BATCH");
+    max_batch_ = env ? std::max(1, std::min(kMaxBatch, atoi(env))) : kMaxBatch;
+  }
+  spec_budget_ = std::max(2 * kMaxBatch, (L - 1) / 2);
+  const int max_expansions = (L - 1) + spec_budget_;
+  max_nodes_ = 1 + 2 * max_expansions;
+  flag_stride_ = n_ / 32 + 2 * kPartThreads;
+  d_flags_.Alloc(static_cast<size_t>(flag_stride_) * kMaxBatch);
+  d_part_counts_.AllocZero(static_cast<size_t>(kPartBlocks) * kMaxBatch);
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
-  d_hist_pool_.Alloc(hist_elems * L);
-  d_hist_work_.Alloc(hist_elems);
-  d_leaves_.AllocZero(L);
-  d_ctrl_.AllocZero(1);
-  d_feat_best_.Alloc(static_cast<size_t>(2) * std::max(F_, 1));
-  d_splittable_.Alloc(static_cast<size_t>(L + 2) * std::max(F_, 1));   // + 2 scratch rows (k_find)
-  d_sorted_leaf_.AllocZero(2 * L);
+  d_hist_pool_.Alloc(hist_elems * (1 + max_expansions));
+  d_hist_work_.Alloc(hist_elems * kMaxBatch);
+  work_elems_ = static_cast<int>(hist_elems);
+  LGB_CUDA(cudaMalloc(&d_nodes_, sizeof(NodeDev) * max_nodes_));
+  LGB_CUDA(cudaMalloc(&d_ctrl_, sizeof(BatchCtrl)));
+  LGB_CUDA(cudaMemset(d_ctrl_, 0, sizeof(BatchCtrl)));
+  d_avail_.AllocZero(L);
+  d_feat_best_.Alloc(static_cast<size_t>(2) * kMaxBatch * std::max(F_, 1));
+  d_splittable_.Alloc(static_cast<size_t>(max_nodes_) * std::max(F_, 1));
+  d_sorted_leaf_.AllocZero(3 * L);
   // tree arrays blob: 8 int arrays [L], decision_type [L], split_gain [L], 4 double arrays [L]
   {
     const size_t ints = 8 * sizeof(int) * L, chars = RoundUp<size_t>(L, 8), floats = RoundUp<size_t>(sizeof(float) * L, 8), dbl = 4 * sizeof(double) * L;
@@ -120,25 +133,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
   }
-#define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_hist<RR, BPL, FLT, false>, kHistSmem)
+#define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
 #undef SET_HIST_SMEM
-#define SET_TREE_SMEM(RR, BPL, FLT) SetSmem(k_tree<RR, BPL, FLT>, kHistSmem)
-  SET_TREE_SMEM(4, 4, false); SET_TREE_SMEM(2, 4, false); SET_TREE_SMEM(1, 4, false);
-  SET_TREE_SMEM(4, 2, true); SET_TREE_SMEM(2, 2, true); SET_TREE_SMEM(1, 2, true);
-#undef SET_TREE_SMEM
-  {
-    // the persistent tree kernel needs every CTA resident at once (cooperative launch): one CTA per SM
-    int dev_sms = 0, coop = 0;
-    LGB_CUDA(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, device_));
-    LGB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_));
-    int per_sm = 0;
-    LGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tree<4, 4, false>, kTreeThreads, kHistSmem));
-    tree_grid_ = (coop && per_sm >= 1) ? dev_sms : 0;
-    const char* env = getenv("LGB_B200_MULTI_KERNEL");
-    if (env != nullptr && env[0] == '1') tree_grid_ = 0;
-  }
   LGB_CUDA(cudaStreamSynchronize(stream_));
   prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
@@ -146,6 +144,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
 Booster::~Booster() {
   cudaSetDevice(device_);
   try { ProfReport(); } catch (...) {}
+  if (d_nodes_) cudaFree(d_nodes_);
+  if (d_ctrl_) cudaFree(d_ctrl_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
   for (auto& e : hist_events_) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (timer_ev_[0]) { cudaEventDestroy(timer_ev_[0]); cudaEventDestroy(timer_ev_[1]); }
@@ -172,10 +172,6 @@ void Booster::ProfReport() {
     cudaEventDestroy(r.a); cudaEventDestroy(r.b);
   }
   prof_recs_.clear();
-  if (prof_phase_[0] > 0) {
-    static const char* kNames[6] = {"tree(all)", "hist", "find", "select", "part_count", "part_scatter"};
-    for (int k = 0; k < 6; ++k) fprintf(stderr, "[prof] tree phase %-14s %6.1f %% of tree cycles\n", kNames[k], 100.0 * prof_phase_[k] / prof_phase_[0]);
-  }
   for (auto& kv : agg) fprintf(stderr, "[prof] %-16s n=%6d total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second, 1e3 * kv.second.second / kv.second.first);
 }
 
@@ -301,11 +297,11 @@ void Booster::ComputeGradients() {
 void Booster::PrepareGradients() {
   const int n = static_cast<int>(n_);
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
-  k_absmax<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_.p);
-  if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_.p->max_abs_g_bits, 2, stream_);
-  k_scales<<<1, 1, 0, stream_>>>(d_ctrl_.p, lp_);
-  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_.p, lp_, static_cast<unsigned int>(iter_),
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
+  k_absmax<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_);
+  if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
+  k_scales<<<1, 1, 0, stream_>>>(d_ctrl_, lp_);
+  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
                                         static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p);
   LGB_CUDA(cudaGetLastError());
   launches_ += 3;
@@ -319,7 +315,7 @@ void Booster::LaunchHist(bool root) {
   const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
   const int tiles = CeilDiv(F_, ft);
   const int row_ctas = std::max(1, kNumSms / tiles);
-  dim3 grid(row_ctas, tiles);
+  dim3 grid(row_ctas, tiles, root ? 1 : max_batch_);
   int rows_per_flush;
   if (flt) {
     rows_per_flush = kFixRowsPerCopy * R;
@@ -328,8 +324,8 @@ void Booster::LaunchHist(bool root) {
     const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
     rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
   }
-  // non-root launches find `work` already cleared by k_part_scatter
-  if (root) LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, d_hist_work_.bytes(), stream_));
+  // non-root launches find their work areas already cleared by k_bt_part_scatter
+  if (root) LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, sizeof(long long) * work_elems_, stream_));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (time_hist_) {
     if (hist_events_used_ == hist_events_.size()) {
@@ -342,11 +338,11 @@ void Booster::LaunchHist(bool root) {
     LGB_CUDA(cudaEventRecord(e0, stream_));
   }
 #define LAUNCH_HIST_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, d_idx_[0].p, d_idx_[1].p, \
-                         d_leaves_.p, d_ctrl_.p, d_hist_work_.p, F_, rows_per_flush
-#define LAUNCH_HIST(RR, BPL, FLT)                                                                              \
-  do {                                                                                                         \
-    if (root) LaunchPdl(k_hist<RR, BPL, FLT, true>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);   \
-    else LaunchPdl(k_hist<RR, BPL, FLT, false>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);       \
+                         d_nodes_, d_ctrl_, d_hist_work_.p, work_elems_, F_, rows_per_flush, row_ctas
+#define LAUNCH_HIST(RR, BPL, FLT)                                                                                     \
+  do {                                                                                                                \
+    if (root) LaunchPdl(k_bt_hist<RR, BPL, FLT, true>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);  \
+    else LaunchPdl(k_bt_hist<RR, BPL, FLT, false>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);      \
   } while (0)
   if (!flt) {
     if (R == 4) LAUNCH_HIST(4, 4, false); else if (R == 2) LAUNCH_HIST(2, 4, false); else LAUNCH_HIST(1, 4, false);
@@ -358,124 +354,85 @@ void Booster::LaunchHist(bool root) {
   LGB_CUDA(cudaGetLastError());
   if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
   ++launches_;
-  if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, d_hist_work_.n, stream_);
+  // data-parallel learner: every rank needs the global histograms of the batch (integer sums: order-independent)
+  if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, static_cast<size_t>(work_elems_) * (root ? 1 : max_batch_), stream_);
 }
 
 void Booster::LaunchFind(bool root) {
-  dim3 grid(F_, root ? 1 : 2);
+  dim3 grid(F_, root ? 1 : 2, root ? 1 : max_batch_);
   if (lp_.quantized)
-    LaunchPdl(k_find<true>, grid, dim3(256), 0, stream_, d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p,
-              d_feat_best_.p, d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+    LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, d_hist_work_.p, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0);
   else
-    LaunchPdl(k_find<false>, grid, dim3(256), 0, stream_, d_hist_work_.p, d_hist_pool_.p, ds_->d_fmeta.p, d_leaves_.p, d_ctrl_.p,
-              d_feat_best_.p, d_splittable_.p, tree_dev_, lp_, root ? 1 : 0);
+    LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, d_hist_work_.p, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0);
   ++launches_;
 }
 
-// Single-GPU learner: the whole tree in one cooperative launch (tree_kernel.cuh).
-bool Booster::TrainTreePersistent() {
-  const BinLayout& lay = ds_->layout;
-  const int R = lay.rows_per_step;
-  const bool flt = !lp_.quantized;
-  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
-  const int tiles = CeilDiv(F_, ft);
-  if (tree_grid_ <= 0 || net_->active() || tiles > tree_grid_) return false;
-  TreeKernelArgs a;
-  a.rm = ds_->d_rm.p; a.rm_stride = static_cast<unsigned>(lay.rm_stride); a.cm = ds_->d_cm.p; a.n_pad = ds_->n_pad;
-  a.fmeta = ds_->d_fmeta.p; a.gh16 = d_gh16_.p; a.ghfix = d_ghfix_.p; a.idx0 = d_idx_[0].p; a.idx1 = d_idx_[1].p; a.es = idx_es_;
-  a.flags = d_flags_.p; a.part_counts = d_part_counts_.p; a.work = d_hist_work_.p; a.pool = d_hist_pool_.p;
-  a.leaves = d_leaves_.p; a.ctrl = d_ctrl_.p; a.feat_best = d_feat_best_.p; a.splittable = d_splittable_.p;
-  a.T = tree_dev_; a.P = lp_; a.F = F_; a.work_elems = static_cast<int>(d_hist_work_.n);
-  if (flt) {
-    a.rows_per_flush = kFixRowsPerCopy * R;
-  } else {
-    const int qb = cfg_.num_grad_quant_bins;
-    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
-    a.rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
+// One round = expand every leaf of the current batch (partition, histogram of the smaller child, split search for both
+// children), then replay the sequential order and choose the next batch.  Every kernel reads its work from device memory
+// and returns at once when the tree is finished, so rounds are enqueued without waiting for the GPU.
+void Booster::EnqueueRounds(int rounds) {
+  for (int r = 0; r < rounds; ++r) {
+    ProfBegin("part_count");
+    LaunchPdl(k_bt_part_count, dim3(kPartBlocks, max_batch_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+              d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_, d_flags_.p, static_cast<long long>(flag_stride_), d_part_counts_.p);
+    ProfEnd();
+    ProfBegin("part_scatter");
+    LaunchPdl(k_bt_part_scatter, dim3(kPartBlocks, max_batch_), dim3(kPartThreads), 0, stream_, d_idx_[0].p, d_idx_[1].p, d_idx_[0].p,
+              d_idx_[1].p, idx_es_, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_flags_.p, static_cast<long long>(flag_stride_),
+              d_part_counts_.p, d_hist_work_.p, work_elems_, lp_);
+    ProfEnd();
+    ProfBegin("hist"); LaunchHist(false); ProfEnd();
+    ProfBegin("find"); LaunchFind(false); ProfEnd();
+    ProfBegin("select");
+    LaunchPdl(k_bt_select, dim3(1), dim3(256), 0, stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
+              spec_budget_, max_batch_);
+    ProfEnd();
+    launches_ += 3;
   }
-  a.n_local = static_cast<int>(n_); a.n_global = static_cast<int>(n_global_);
-  void* args[] = {&a};
-  const void* fn = nullptr;
-  if (!flt) fn = R == 4 ? (const void*)k_tree<4, 4, false> : R == 2 ? (const void*)k_tree<2, 4, false> : (const void*)k_tree<1, 4, false>;
-  else fn = R == 4 ? (const void*)k_tree<4, 2, true> : R == 2 ? (const void*)k_tree<2, 2, true> : (const void*)k_tree<1, 2, true>;
-  ProfBegin("tree");
-  if (time_hist_) {      // one event pair around the whole tree; the histogram share comes from the kernel's own cycle counters
-    if (hist_events_.empty()) {
-      cudaEvent_t e0, e1;
-      LGB_CUDA(cudaEventCreate(&e0)); LGB_CUDA(cudaEventCreate(&e1));
-      hist_events_.emplace_back(e0, e1);
-    }
-    LGB_CUDA(cudaEventRecord(hist_events_[0].first, stream_));
-  }
-  LGB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(tree_grid_), dim3(kTreeThreads), args, kHistSmem, stream_));
-  if (time_hist_) { LGB_CUDA(cudaEventRecord(hist_events_[0].second, stream_)); tree_event_pending_ = true; }
-  ProfEnd();
-  ++launches_;
-  return true;
 }
 
-// Multi-kernel path (data-parallel learner, or when the persistent kernel cannot be used).
-// One tree = a fixed sequence of launches with device-resident control flow (no host round trip until the tree is read back):
-//   root: hist -> find(+select);  per split: part_count -> part_scatter -> hist(smaller child) -> find(+select)
 void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
   hist_events_used_ = 0;
-  if (TrainTreePersistent()) {
-    FetchTree(out);
-    return;
-  }
-  k_tree_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, L, n, static_cast<int>(n_global_));
+  k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
-  for (int split = 0; split < L - 1; ++split) {
-    ProfBegin("part_count");
-    LaunchPdl(k_part_count, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-              d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_.p, d_flags_.p, d_part_counts_.p);
-    ProfEnd();
-    ProfBegin("part_scatter");
-    LaunchPdl(k_part_scatter, dim3(kPartBlocks), dim3(kPartThreads), 0, stream_, d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p,
-              idx_es_, d_gh16_.p, d_ghfix_.p, d_ctrl_.p, d_leaves_.p, d_flags_.p, d_part_counts_.p, tree_dev_, d_hist_work_.p, static_cast<int>(d_hist_work_.n), lp_);
-    ProfEnd();
-    launches_ += 2;
-    if (split < L - 2) {
-      ProfBegin("hist"); LaunchHist(false); ProfEnd();
-      ProfBegin("find"); LaunchFind(false); ProfEnd();
-    }
+  ProfBegin("select");
+  LaunchPdl(k_bt_select, dim3(1), dim3(256), 0, stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
+            spec_budget_, max_batch_);
+  ProfEnd();
+  ++launches_;
+  // the number of rounds a tree needs is only known on the device: enqueue as many as the previous tree used (+1), then look
+  int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + 1) : std::min(L - 1, (L - 1) / 2 + 2);
+  int total = 0;
+  while (true) {
+    EnqueueRounds(rounds);
+    total += rounds;
+    LGB_CUDA(cudaGetLastError());
+    if (FetchTree(out)) break;
+    LGB_CHECK(total < 2 * L, "tree growth did not finish");   // cannot happen: every round commits at least one split
+    rounds = std::max(1, std::min(L - 1, (L - 1) / 4));
   }
-  LGB_CUDA(cudaGetLastError());
-  FetchTree(out);
 }
 
-void Booster::FetchTree(HostTree* t) {
+// Copies the control block and the tree arrays back; false when the tree is not finished yet (more rounds are needed).
+bool Booster::FetchTree(HostTree* t) {
   const int L = cfg_.num_leaves;
-  TreeCtrl hc;
+  BatchCtrl hc;
   LGB_CUDA(cudaMemcpyAsync(h_tree_blob_.data(), d_tree_blob_.p, tree_blob_bytes_, cudaMemcpyDeviceToHost, stream_));
-  LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_.p, sizeof(TreeCtrl), cudaMemcpyDeviceToHost, stream_));
+  LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, stream_));
   Sync();
+  if (!hc.done) return false;
+  last_rounds_ = hc.rounds;
+  rounds_total_ += hc.rounds; expansions_total_ += (hc.num_nodes - 1) / 2; splits_total_ += hc.num_leaves - 1;
   last_rows_visited_ += hc.hist_rows;
   hist_launches_ += hc.hist_launches;
-  if (tree_event_pending_) {
-    float ms = 0;
-    LGB_CUDA(cudaEventElapsedTime(&ms, hist_events_[0].first, hist_events_[0].second));
-    if (hc.tree_cycles > 0) last_hist_ms_ += ms * static_cast<double>(hc.hist_cycles) / static_cast<double>(hc.tree_cycles);
-    tree_event_pending_ = false;
-  }
-  if (prof_ && hc.tree_cycles > 0 && iter_ == 10) {
-    fprintf(stderr, "[dbg] empty grid.sync = %lld cycles\n", hc.dbg[191]);
-    for (int i = 0; i < 30; ++i)
-      fprintf(stderr, "[dbg] split %2d smaller_rows=%8lld hist=%7lld find=%6lld select=%6lld count=%6lld scatter=%6lld cycles\n", i,
-              hc.dbg[i * 6 + 0], hc.dbg[i * 6 + 1], hc.dbg[i * 6 + 2], hc.dbg[i * 6 + 3], hc.dbg[i * 6 + 4], hc.dbg[i * 6 + 5]);
-  }
-  if (prof_ && hc.tree_cycles > 0) {
-    static const char* kNames[6] = {"init", "hist", "find", "select", "part_count", "part_scatter"};
-    for (int k = 1; k < 6; ++k) prof_phase_[k] += static_cast<double>(hc.phase_cycles[k]);
-    prof_phase_[0] += static_cast<double>(hc.tree_cycles);
-    (void)kNames;
-  }
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_.p->hist_rows, 0, 12 * sizeof(long long), stream_));
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_->hist_rows, 0, 2 * sizeof(long long), stream_));
   const int nl = hc.num_leaves;
   t->num_leaves = nl;
   t->shrinkage = 1.0;
@@ -500,14 +457,16 @@ void Booster::FetchTree(HostTree* t) {
     t->split_feature[i] = ds_->used[inner];
     t->threshold[i] = ds_->mappers[ds_->used[inner]].upper[t->threshold_in_bin[i]];   // RealThreshold
   }
+  return true;
 }
 
 void Booster::UpdateScores() {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
-  k_sort_leaves<<<1, 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, d_sorted_leaf_.p, L);
-  k_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, idx_es_, d_leaves_.p, d_ctrl_.p,
-                                                                             d_sorted_leaf_.p, L, tree_dev_.leaf_value, cfg_.learning_rate, n);
+  k_bt_sort_leaves<<<1, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_sorted_leaf_.p, L);
+  k_bt_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_,
+                                                                                d_sorted_leaf_.p, L, tree_dev_.leaf_value,
+                                                                                cfg_.learning_rate, n);
   LGB_CUDA(cudaGetLastError());
   launches_ += 2;
 }
@@ -632,8 +591,8 @@ void Booster::CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const {
   std::vector<uint16_t> tmp(n_);
   LGB_CUDA(cudaMemcpy(tmp.data(), d_gh16_.p, sizeof(uint16_t) * n_, cudaMemcpyDeviceToHost));
   for (int64_t i = 0; i < n_; ++i) { g[i] = static_cast<int8_t>(tmp[i] >> 8); h[i] = static_cast<int8_t>(tmp[i] & 0xff); }
-  TreeCtrl hc;
-  LGB_CUDA(cudaMemcpy(&hc, d_ctrl_.p, sizeof(TreeCtrl), cudaMemcpyDeviceToHost));
+  BatchCtrl hc;
+  LGB_CUDA(cudaMemcpy(&hc, d_ctrl_, sizeof(BatchCtrl), cudaMemcpyDeviceToHost));
   scales[0] = hc.grad_scale; scales[1] = hc.hess_scale;
 }
 
@@ -648,11 +607,11 @@ void Booster::PredictRaw(const double* data, int nrow, int ncol, double* out) co
 
 void Booster::DebugRootHistogram(long long* out) {
   LGB_CUDA(cudaSetDevice(device_));
-  k_tree_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, cfg_.num_leaves,
-                                                                    static_cast<int>(n_), static_cast<int>(n_global_));
+  k_bt_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, cfg_.num_leaves,
+                                                                  static_cast<int>(n_), static_cast<int>(n_global_));
   LaunchHist(true);
   Sync();
-  LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, d_hist_work_.bytes(), cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
 }
 
 void Booster::TimerStart() {
@@ -672,8 +631,8 @@ float Booster::TimerStop() {
 
 float Booster::TimeRootHistogram(int repeats) {
   LGB_CUDA(cudaSetDevice(device_));
-  k_tree_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_leaves_.p, d_ctrl_.p, tree_dev_, cfg_.num_leaves,
-                                                                    static_cast<int>(n_), static_cast<int>(n_global_));
+  k_bt_init<<<CeilDiv(cfg_.num_leaves, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, cfg_.num_leaves,
+                                                                  static_cast<int>(n_), static_cast<int>(n_global_));
   const bool was = time_hist_;
   time_hist_ = true;
   float total = 0;

@@ -12,6 +12,11 @@
 #include "network.h"
 
 namespace lgb {
+struct NodeDev;
+struct BatchCtrl;
+}  // namespace lgb
+
+namespace lgb {
 
 struct SplitDev {
   double gain;
@@ -35,24 +40,11 @@ struct LeafDev {
   SplitDev best;
 };
 
+// Descriptors of the stand-alone histogram kernel k_hist (hist_kernel.cuh), used by the allocation-free entry point.
 struct TreeCtrl {
-  int num_leaves;
-  int done;
-  int cur_leaf, new_leaf, cur_node;
-  int cur_feature, cur_threshold, cur_default_left, cur_nan_bin;
-  int src_begin, src_count, src_buf;
-  int smaller, larger, find, pending;
-  int parent_slot;
-  int find_count[2];                // CTAs of k_find that finished, per child (last-CTA reductions)
-  int find_children_done;
-  unsigned int max_abs_g_bits, max_abs_h_bits;
-  double grad_scale, hess_scale;      // quantized: int -> float scales.  float mode: fixed-point -> float (powers of two)
-  double inv_grad_scale, inv_hess_scale;
-  long long hist_rows;              // rows visited by histogram launches since the host last cleared it
-  long long hist_launches;          // histogram launches that did work since the host last cleared it
-  long long phase_cycles[8];          // persistent kernel, CTA 0: init, hist, find, select, count, scatter
-  long long hist_cycles, tree_cycles;
-  long long dbg[192];                 // development aid: per split (rows, hist cycles, count cycles, scatter cycles, find, select)   // persistent kernel: SM cycles CTA 0 spent in histogram phases / in the whole tree
+  int done, find, smaller;
+  int pad_;
+  long long hist_rows, hist_launches;
 };
 
 struct TreeArraysDev {
@@ -92,6 +84,9 @@ class Booster {
   float TimeRootHistogram(int repeats);
   int64_t last_hist_rows_visited() const { return last_rows_visited_; }
   int64_t hist_launches() const { return hist_launches_; }
+  int64_t growth_rounds() const { return rounds_total_; }
+  int64_t growth_expansions() const { return expansions_total_; }
+  int64_t growth_splits() const { return splits_total_; }
   double last_hist_ms() const { return last_hist_ms_; }
   int launches() const { return launches_; }
   void EnableHistTiming(bool on) { time_hist_ = on; }
@@ -122,8 +117,10 @@ class Booster {
   DevBuf<unsigned int> d_flags_;
   DevBuf<int> d_part_counts_;
   DevBuf<long long> d_hist_pool_, d_hist_work_;
-  DevBuf<LeafDev> d_leaves_;
-  DevBuf<TreeCtrl> d_ctrl_;
+  NodeDev* d_nodes_ = nullptr;       // [max_nodes_]
+  BatchCtrl* d_ctrl_ = nullptr;
+  DevBuf<int> d_avail_;              // leaf id of the committed tree -> node
+  int max_nodes_ = 0, spec_budget_ = 0, max_batch_ = 4, last_rounds_ = 0;
   DevBuf<SplitDev> d_feat_best_;     // [2][F]
   DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
   DevBuf<unsigned char> d_tree_blob_;
@@ -139,17 +136,17 @@ class Booster {
   // measurement
   bool time_hist_ = false;
   int64_t last_rows_visited_ = 0, hist_launches_ = 0;
+  int64_t rounds_total_ = 0, expansions_total_ = 0, splits_total_ = 0;   // batched growth statistics over all trees
   double last_hist_ms_ = 0;
   int launches_ = 0;
-  bool tree_event_pending_ = false;
+  long long flag_stride_ = 0;
+  int work_elems_ = 0;
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
-  int tree_grid_ = 0;               // CTAs of the persistent tree kernel (0: not available)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;
   cudaEvent_t timer_ev_[2] = {nullptr, nullptr};
   // per-kernel-type timing with CUDA events (LGB_B200_PROFILE=1): development aid, breaks launch overlap
   bool prof_ = false;
-  double prof_phase_[6] = {0, 0, 0, 0, 0, 0};
   struct ProfRec { const char* name; cudaEvent_t a, b; };
   std::vector<ProfRec> prof_recs_;
   void ProfBegin(const char* name);
@@ -163,8 +160,8 @@ class Booster {
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
   void LaunchFind(bool root);
-  bool TrainTreePersistent();
-  void FetchTree(HostTree* out);
+  void EnqueueRounds(int rounds);
+  bool FetchTree(HostTree* out);
   void UpdateScores();
   ModelHeader MakeHeader() const;
   void Sync() const;

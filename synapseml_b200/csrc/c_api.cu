@@ -322,6 +322,14 @@ int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, 
   *hist_rows_visited = b->last_hist_rows_visited(); *hist_ms = b->last_hist_ms(); *kernel_launches = b->launches(); *hist_launches = b->hist_launches();
   API_END();
 }
+// Batched best-first growth, summed over all trees so far: rounds = dependent expand rounds, expansions = leaves expanded
+// (partition + histogram + split search), splits = expansions that ended up in a tree.
+int LGBM_B200_BoosterGetGrowthStats(BoosterHandle handle, int64_t* rounds, int64_t* expansions, int64_t* splits) {
+  API_BEGIN();
+  auto b = static_cast<Booster*>(handle);
+  *rounds = b->growth_rounds(); *expansions = b->growth_expansions(); *splits = b->growth_splits();
+  API_END();
+}
 // TCP hand-off used by LGBM_NetworkInit to distribute the NCCL unique id, exposed so the multi-process path can be tested
 // without GPUs: rank 0 (first entry of `machines`) sends `blob`, every other rank receives it in place.
 int LGBM_B200_NetworkBootstrapBlob(const char* machines, int local_listen_port, int listen_time_out, uint8_t* blob, int32_t bytes,
