@@ -57,6 +57,9 @@ struct BatchCtrl {
   long long batch_rows;    // rows of all smaller children of the current batch (histogram CTAs are shared out by it)
   BatchItem batch[kMaxBatch];
   int find_count[kMaxBatch][2];
+  unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
+  int part_ctas_done;                          // CTAs of the running partition kernel that are finished
+  int pad2_;
   unsigned int max_abs_g_bits, max_abs_h_bits;
   double grad_scale, hess_scale, inv_grad_scale, inv_hess_scale;
   long long hist_rows, hist_launches;
@@ -82,7 +85,8 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
     avail[0] = 0;
     ctrl->num_leaves = 1; ctrl->done = 0; ctrl->num_nodes = 1; ctrl->num_slots = 1; ctrl->batch_n = 0; ctrl->spec_used = 0;
     ctrl->rounds = 0; ctrl->batch_rows = 0;
-    for (int k = 0; k < kMaxBatch; ++k) { ctrl->find_count[k][0] = 0; ctrl->find_count[k][1] = 0; }
+    for (int k = 0; k < kMaxBatch; ++k) { ctrl->find_count[k][0] = 0; ctrl->find_count[k][1] = 0; ctrl->part_cursor[k] = 0ULL; }
+    ctrl->part_ctas_done = 0;
   }
 }
 
@@ -220,279 +224,316 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   }
 }
 
-// ------------------------------------------------------------------------------------------------ K7 (batched)
-__global__ void __launch_bounds__(kPartThreads) k_bt_part_count(const uint8_t* __restrict__ cm, long long n_pad,
-                                                                const int* __restrict__ idx0, const int* __restrict__ idx1, int es,
-                                                                const BatchCtrl* __restrict__ ctrl, unsigned int* __restrict__ flags,
-                                                                long long flag_stride, int* __restrict__ block_counts) {
-  PdlLaunchDependents();
-  PdlWait();
-  if (ctrl->done) return;
-  const int k = blockIdx.y;
-  if (k >= ctrl->batch_n) return;
-  const BatchItem& it = ctrl->batch[k];
-  const int n = it.src_count, begin = it.src_begin, buf = it.src_buf;
-  const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left;
-  const uint8_t* col = cm + static_cast<size_t>(it.feature) * n_pad;
-  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
-  flags += static_cast<size_t>(k) * flag_stride;
-  block_counts += k * gridDim.x;
-  int lo_w, hi_w;
-  PartChunk(n, &lo_w, &hi_w);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NW = kPartThreads / 32;
-  int cnt = 0;
-  for (int w0 = lo_w + warp; w0 < hi_w; w0 += NW * 4) {
-    int rows[4];
-    #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int w = w0 + u * NW;
-      const int p = w * 32 + lane;
-      rows[u] = (w < hi_w && p < n) ? (idx ? idx[static_cast<size_t>(begin + p) * es] : begin + p) : -1;
-    }
-    int bins[4];
-    #pragma unroll
-    for (int u = 0; u < 4; ++u) bins[u] = rows[u] >= 0 ? col[rows[u]] : -1;
-    #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int w = w0 + u * NW;
-      const bool left = rows[u] >= 0 && ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr));
-      const unsigned int word = __ballot_sync(0xffffffffu, left);
-      if (lane == 0 && w < hi_w) { flags[w] = word; cnt += __popc(word); }
-    }
-  }
-  __shared__ int s_cnt[NW];
-  if (lane == 0) s_cnt[warp] = cnt;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int t = 0;
-    for (int i = 0; i < NW; ++i) t += s_cnt[i];
-    block_counts[blockIdx.x] = t;
-  }
+// ------------------------------------------------------------------------------------------------ K7 (batched, one pass)
+// All leaves of the batch are cut into tiles of kPartTileRows rows; the CTAs walk the concatenated tile list, so the work is
+// balanced whatever the leaf sizes are.  A tile reads its index entries once, looks up the split feature's bin of each row
+// (column-major copy), reserves room for its lefts and rights with ONE 64-bit atomic on the leaf's cursor (left count in the
+// high word, right count in the low word) and writes the entries to the other index buffer: lefts grow from the front of
+// the parent's range, rights from its back.  Inside a tile the order is kept; tiles land in the order their atomics arrive.
+// Every sum taken over a leaf's rows is an exact integer sum (quantized or fixed-point gradients), so the order of rows
+// inside a leaf does not change any result.  The last tile of a leaf publishes the two children.
+constexpr int kPartTileWords = 64;                        // 8 words per warp, 8 warps
+constexpr int kPartTileRows = kPartTileWords * 32;
+
+// Publishes the two children of batch item k once all its rows are placed (what DataPartition::Split and the leaf-splits
+// initialisation do in the reference learner).  One thread.
+__device__ __forceinline__ void PublishChildren(BatchCtrl* ctrl, NodeDev* nodes, int k, const LearnerParams& P) {
+  const BatchItem it = ctrl->batch[k];
+  const int n = it.src_count, begin = it.src_begin;
+  const int other = it.src_buf < 0 ? 0 : 1 - it.src_buf;
+  const unsigned long long cur = atomicAdd(&ctrl->part_cursor[k], 0ULL);
+  const int total = static_cast<int>(cur >> 32);
+  const NodeDev par = nodes[it.node];
+  const SplitDev bs = par.best;
+  const int nl_true = total, nr_true = n - total;
+  int lc = bs.left_count, rc = bs.right_count;
+  if (!P.dp) { lc = nl_true; rc = nr_true; }       // serial learner: true partition counts replace the estimates
+  NodeDev L, Rr;
+  const int depth = par.depth + 1;
+  L.begin = begin; L.count = nl_true; L.buf = other; L.global_count = lc;
+  L.int_g = bs.left_int_g; L.int_h = bs.left_int_h; L.sum_g = bs.left_sum_g; L.sum_h = bs.left_sum_h; L.depth = depth;
+  Rr.begin = begin + nl_true; Rr.count = nr_true; Rr.buf = other; Rr.global_count = rc;
+  Rr.int_g = bs.right_int_g; Rr.int_h = bs.right_int_h; Rr.sum_g = bs.right_sum_g; Rr.sum_h = bs.right_sum_h; Rr.depth = depth;
+  L.state = Rr.state = 0; L.left = L.right = Rr.left = Rr.right = -1; L.pad_ = Rr.pad_ = 0;
+  L.best = EmptySplit(-1, -1); Rr.best = EmptySplit(-1, -1);
+  const bool left_smaller = lc < rc;
+  const int fresh_slot = atomicAdd(&ctrl->num_slots, 1);
+  // the larger child takes over the parent's pool slot (parent - smaller is formed in place), the smaller gets a fresh one
+  L.hist_slot = left_smaller ? fresh_slot : par.hist_slot;
+  Rr.hist_slot = left_smaller ? par.hist_slot : fresh_slot;
+  bool find = true;                                  // BeforeFindBestSplit
+  if (P.max_depth > 0 && depth >= P.max_depth) find = false;
+  if (rc < P.min_data_in_leaf * 2 && lc < P.min_data_in_leaf * 2) find = false;
+  nodes[it.left] = L; nodes[it.right] = Rr;
+  nodes[it.node].state = 1; nodes[it.node].left = it.left; nodes[it.node].right = it.right;
+  ctrl->batch[k].smaller = left_smaller ? it.left : it.right;
+  ctrl->batch[k].larger = left_smaller ? it.right : it.left;
+  ctrl->batch[k].find = find ? 1 : 0;
+  if (find) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->batch_rows), static_cast<unsigned long long>(left_smaller ? nl_true : nr_true));
 }
 
-__global__ void __launch_bounds__(kPartThreads) k_bt_part_scatter(const int* __restrict__ idx0r, const int* __restrict__ idx1r,
-                                                                  int* __restrict__ idx0w, int* __restrict__ idx1w, int es,
-                                                                  const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-                                                                  BatchCtrl* __restrict__ ctrl, NodeDev* __restrict__ nodes,
-                                                                  const unsigned int* __restrict__ flags, long long flag_stride,
-                                                                  const int* __restrict__ block_counts, long long* __restrict__ work,
-                                                                  int work_elems, LearnerParams P) {
+template <int ES>
+__global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t* __restrict__ cm, long long n_pad,
+                                                               const int* __restrict__ idx0r, const int* __restrict__ idx1r,
+                                                               int* __restrict__ idx0w, int* __restrict__ idx1w,
+                                                               const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+                                                               BatchCtrl* __restrict__ ctrl, NodeDev* __restrict__ nodes,
+                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
   PdlLaunchDependents();
   PdlWait();
   if (ctrl->done) return;
-  const int k = blockIdx.y;
-  if (k >= ctrl->batch_n) return;
-  // the histogram of this item accumulates into work[k] with atomics: clear it here
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < work_elems; i += gridDim.x * blockDim.x)
-    work[static_cast<size_t>(k) * work_elems + i] = 0;
-  const BatchItem it = ctrl->batch[k];
-  const int n = it.src_count, begin = it.src_begin, buf = it.src_buf;
-  const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
-  const int other = buf < 0 ? 0 : 1 - buf;
-  int* dst = other == 0 ? idx0w : idx1w;
-  flags += static_cast<size_t>(k) * flag_stride;
-  block_counts += k * gridDim.x;
+  const int bn = ctrl->batch_n;
   constexpr int NW = kPartThreads / 32;
-  __shared__ int s_red[2][NW];
-  __shared__ int s_prefix[kPartWordsPerIter];
-  __shared__ int s_carry;
+  constexpr int WPW = kPartTileWords / NW;      // words per warp
+  __shared__ int s_tiles[kMaxBatch + 1];
+  __shared__ int s_wl[NW], s_wv[NW];
+  __shared__ unsigned long long s_base;
+  __shared__ int s_lastcta;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int before = 0, total = 0;
-  for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
-    const int c = block_counts[i];
-    total += c;
-    if (i < blockIdx.x) before += c;
+  // the histograms of this batch accumulate into work[0..bn) with atomics: clear them here
+  for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < static_cast<size_t>(bn) * work_elems; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    work[i] = 0;
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < kMaxBatch; ++k) {
+      s_tiles[k] = t;
+      if (k < bn) t += max(1, (ctrl->batch[k].src_count + kPartTileRows - 1) / kPartTileRows);
+    }
+    s_tiles[kMaxBatch] = t;
   }
-  for (int o = 16; o > 0; o >>= 1) { before += __shfl_xor_sync(0xffffffffu, before, o); total += __shfl_xor_sync(0xffffffffu, total, o); }
-  if (lane == 0) { s_red[0][warp] = before; s_red[1][warp] = total; }
   __syncthreads();
-  before = 0; total = 0;
-  for (int i = 0; i < NW; ++i) { before += s_red[0][i]; total += s_red[1][i]; }
-  int lo_w, hi_w;
-  PartChunk(n, &lo_w, &hi_w);
-  if (threadIdx.x == 0) s_carry = before;
-  __syncthreads();
-  for (int base_w = lo_w; base_w < hi_w; base_w += kPartWordsPerIter) {
-    const int nw = min(kPartWordsPerIter, hi_w - base_w);
-    for (int t0 = 0; t0 < nw; t0 += kPartThreads) {
-      const int t = t0 + threadIdx.x;
-      int c = t < nw ? __popc(flags[base_w + t]) : 0;
-      int incl = c;
-      for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
-      if (lane == 31) s_red[0][warp] = incl;
-      __syncthreads();
-      int wp = 0, tot = 0;
-      for (int i = 0; i < NW; ++i) { if (i < warp) wp += s_red[0][i]; tot += s_red[0][i]; }
-      if (t < nw) s_prefix[t] = s_carry + wp + incl - c;
-      __syncthreads();
-      if (threadIdx.x == 0) s_carry += tot;
-      __syncthreads();
-    }
-    for (int w0 = warp; w0 < nw; w0 += NW * 4) {
-      int4 ent[4];
-      #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int w = w0 + u * NW;
-        const int p = (base_w + w) * 32 + lane;
-        ent[u] = make_int4(-1, 0, 0, 0);
-        if (w < nw && p < n) {
-          if (idx) {
-            if (es == 2) { const int2 e = reinterpret_cast<const int2*>(idx)[begin + p]; ent[u].x = e.x; ent[u].y = e.y; }
-            else ent[u] = reinterpret_cast<const int4*>(idx)[begin + p];
-          } else {           // the root: rows are 0..n-1, gradients come from the per-row arrays
-            const int row = begin + p;
-            ent[u].x = row;
-            if (es == 2) {
-              const unsigned int g = gh16[row];
-              ent[u].y = static_cast<int>((static_cast<unsigned>(static_cast<int>(static_cast<signed char>(g >> 8))) << 16) + (g & 0xffu));
-            } else { const int2 g = ghfix[row]; ent[u].y = g.x; ent[u].z = g.y; }
-          }
-        }
-      }
-      #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int w = w0 + u * NW;
-        if (w >= nw) continue;
-        const unsigned int word = flags[base_w + w];
-        const int p = (base_w + w) * 32 + lane;
-        if (ent[u].x >= 0) {
-          const int lefts_before = s_prefix[w] + __popc(word & ((1u << lane) - 1u));
-          const int pos = ((word >> lane) & 1u) ? begin + lefts_before : begin + total + (p - lefts_before);
-          if (es == 2) reinterpret_cast<int2*>(dst)[pos] = make_int2(ent[u].x, ent[u].y);
-          else reinterpret_cast<int4*>(dst)[pos] = ent[u];
+  const int total_tiles = s_tiles[kMaxBatch];
+  // A tile is a chain of three dependent memory round trips (entries -> bins -> cursor atomic) before its stores; what hides
+  // them is the number of tiles in flight per SM (4 CTAs of 8 rows per thread: 8192 rows), not anything inside one CTA.
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    int k = 0;
+    while (k + 1 < bn && tile >= s_tiles[k + 1]) ++k;
+    const BatchItem& it = ctrl->batch[k];
+    const int n = it.src_count, begin = it.src_begin, buf = it.src_buf;
+    const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left;
+    const uint8_t* col = cm + static_cast<size_t>(it.feature) * n_pad;
+    const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
+    int* dst = (buf < 0 ? 0 : 1 - buf) == 0 ? idx0w : idx1w;
+    const int p_base = (tile - s_tiles[k]) * kPartTileRows + warp * (WPW * 32) + lane;
+    int4 ent[WPW];
+    #pragma unroll
+    for (int u = 0; u < WPW; ++u) {
+      const int p = p_base + u * 32;
+      ent[u] = make_int4(-1, 0, 0, 0);
+      if (p < n) {
+        if (idx) {
+          if (ES == 2) { const int2 e = reinterpret_cast<const int2*>(idx)[begin + p]; ent[u].x = e.x; ent[u].y = e.y; }
+          else ent[u] = reinterpret_cast<const int4*>(idx)[begin + p];
+        } else {             // the root: rows are 0..n-1, gradients come from the per-row arrays
+          const int row = begin + p;
+          ent[u].x = row;
+          if (ES == 2) {
+            const unsigned int g = gh16[row];
+            ent[u].y = static_cast<int>((static_cast<unsigned>(static_cast<int>(static_cast<signed char>(g >> 8))) << 16) + (g & 0xffu));
+          } else { const int2 g = ghfix[row]; ent[u].y = g.x; ent[u].z = g.y; }
         }
       }
     }
+    int bins[WPW];
+    #pragma unroll
+    for (int u = 0; u < WPW; ++u) bins[u] = ent[u].x >= 0 ? col[ent[u].x] : -1;
+    unsigned int lmask[WPW], rmask[WPW];
+    int wl = 0, wr = 0;
+    #pragma unroll
+    for (int u = 0; u < WPW; ++u) {
+      const bool valid = ent[u].x >= 0;
+      const bool left = valid && ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr));
+      lmask[u] = __ballot_sync(0xffffffffu, left);
+      rmask[u] = __ballot_sync(0xffffffffu, valid && !left);
+      wl += __popc(lmask[u]); wr += __popc(rmask[u]);
+    }
+    if (lane == 0) { s_wl[warp] = wl; s_wv[warp] = wr; }
     __syncthreads();
+    int lefts_before = 0, rights_before = 0, tile_l = 0, tile_r = 0;
+    #pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      const int a = s_wl[w], v = s_wv[w];
+      if (w < warp) { lefts_before += a; rights_before += v; }
+      tile_l += a; tile_r += v;
+    }
+    if (threadIdx.x == 0)
+      s_base = atomicAdd(&ctrl->part_cursor[k], (static_cast<unsigned long long>(tile_l) << 32) | static_cast<unsigned>(tile_r));
+    __syncthreads();
+    const unsigned long long base = s_base;
+    const int lbase = static_cast<int>(base >> 32), rbase = static_cast<int>(base & 0xffffffffu);
+    // lefts of this tile: [begin + lbase, +tile_l); rights: [begin + n - rbase - tile_r, begin + n - rbase)
+    int lpos = begin + lbase + lefts_before;
+    int rpos = begin + n - rbase - tile_r + rights_before;
+    const unsigned lt = (1u << lane) - 1u;
+    #pragma unroll
+    for (int u = 0; u < WPW; ++u) {
+      if (ent[u].x >= 0) {
+        const bool left = (lmask[u] >> lane) & 1u;
+        const int pos = left ? lpos + __popc(lmask[u] & lt) : rpos + __popc(rmask[u] & lt);
+        if (ES == 2) reinterpret_cast<int2*>(dst)[pos] = make_int2(ent[u].x, ent[u].y);
+        else reinterpret_cast<int4*>(dst)[pos] = ent[u];
+      }
+      lpos += __popc(lmask[u]);
+      rpos += __popc(rmask[u]);
+    }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    // publish the two children (what DataPartition::Split + the leaf-splits initialisation do)
-    const NodeDev par = nodes[it.node];
-    const SplitDev bs = par.best;
-    const int nl_true = total, nr_true = n - total;
-    int lc = bs.left_count, rc = bs.right_count;
-    if (!P.dp) { lc = nl_true; rc = nr_true; }       // serial learner: true partition counts replace the estimates
-    NodeDev L, Rr;
-    const int depth = par.depth + 1;
-    L.begin = begin; L.count = nl_true; L.buf = other; L.global_count = lc;
-    L.int_g = bs.left_int_g; L.int_h = bs.left_int_h; L.sum_g = bs.left_sum_g; L.sum_h = bs.left_sum_h; L.depth = depth;
-    Rr.begin = begin + nl_true; Rr.count = nr_true; Rr.buf = other; Rr.global_count = rc;
-    Rr.int_g = bs.right_int_g; Rr.int_h = bs.right_int_h; Rr.sum_g = bs.right_sum_g; Rr.sum_h = bs.right_sum_h; Rr.depth = depth;
-    L.state = Rr.state = 0; L.left = L.right = Rr.left = Rr.right = -1; L.pad_ = Rr.pad_ = 0;
-    L.best = EmptySplit(-1, -1); Rr.best = EmptySplit(-1, -1);
-    const bool left_smaller = lc < rc;
-    const int fresh_slot = atomicAdd(&ctrl->num_slots, 1);
-    // the larger child takes over the parent's pool slot (parent - smaller is formed in place), the smaller gets a fresh one
-    L.hist_slot = left_smaller ? fresh_slot : par.hist_slot;
-    Rr.hist_slot = left_smaller ? par.hist_slot : fresh_slot;
-    bool find = true;                                  // BeforeFindBestSplit
-    if (P.max_depth > 0 && depth >= P.max_depth) find = false;
-    if (rc < P.min_data_in_leaf * 2 && lc < P.min_data_in_leaf * 2) find = false;
-    nodes[it.left] = L; nodes[it.right] = Rr;
-    nodes[it.node].state = 1; nodes[it.node].left = it.left; nodes[it.node].right = it.right;
-    ctrl->batch[k].smaller = left_smaller ? it.left : it.right;
-    ctrl->batch[k].larger = left_smaller ? it.right : it.left;
-    ctrl->batch[k].find = find ? 1 : 0;
-    if (find) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->batch_rows), static_cast<unsigned long long>(left_smaller ? nl_true : nr_true));
+  // the CTA that finishes last publishes the children of the whole batch
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_lastcta = (atomicAdd(&ctrl->part_ctas_done, 1) == static_cast<int>(gridDim.x) - 1);
+  __syncthreads();
+  if (s_lastcta) {
+    __threadfence();
+    if (threadIdx.x < bn) PublishChildren(ctrl, nodes, threadIdx.x, P);
+    if (threadIdx.x == 0) ctrl->part_ctas_done = 0;
   }
 }
 
 // ------------------------------------------------------------------------------------------------ replay + next batch
+// One CTA.  Global memory is touched in parallel phases only; the order-dependent part of the replay runs on shared copies:
+//   P0  every thread loads one available leaf (its candidate split, whether it is expanded, its children's candidates) and the
+//       per-leaf tree arrays;
+//   P1  warp 0 replays the sequential leaf choice and records the commit list;
+//   P2  thread j writes the order-independent tree fields of commit j and stages the rest;
+//   P3  thread 0 applies the order-dependent bookkeeping of Tree::Split (parent/child links, depths, leaf values) in commit order;
+//   P4  per-leaf arrays are written back and the next batch is chosen.
+struct SelectSmem {
+  double *gain, *cgain0, *cgain1, *lvalue, *lweight, *c_lo, *c_ro, *c_lw, *c_rw;
+  int *feat, *node, *rank, *cfeat0, *cfeat1, *cnode0, *cnode1, *lparent, *ldepth, *lcount, *c_leaf, *c_node, *c_lc, *c_rc;
+  unsigned char *exp, *isleft;
+};
+constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 14 * sizeof(int) + 2;
+__host__ __device__ inline size_t SelectSmemBytes(int L) { return kSelectSmemPerLeaf * static_cast<size_t>((L + 7) & ~7) + 64; }
+
 __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, int* __restrict__ avail, BatchCtrl* __restrict__ ctrl,
                                                    TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
                                                    int max_nodes, int spec_budget, int max_batch) {
   PdlLaunchDependents();
   PdlWait();
   if (ctrl->done) return;
-  __shared__ double s_gain[1024];
-  __shared__ int s_feat[1024], s_node[1024], s_rank[1024];
-  __shared__ unsigned char s_exp[1024];
-  __shared__ double r_gain[8];
-  __shared__ int r_feat[8], r_idx[8];
-  __shared__ int s_best, s_state;      // s_state: 0 keep replaying, 1 finished tree, 2 expansion needed
-  __shared__ int s_count;
+  extern __shared__ double sel_smem_raw[];
+  __shared__ int s_state, s_nl, s_m, s_count;
   const int L = P.num_leaves;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int nl = ctrl->num_leaves;
-  for (int i = tid; i < nl; i += blockDim.x) {
+  const int Lc = (L + 7) & ~7;
+  SelectSmem S;
+  {
+    double* d = sel_smem_raw;
+    S.gain = d; d += Lc; S.cgain0 = d; d += Lc; S.cgain1 = d; d += Lc; S.lvalue = d; d += Lc; S.lweight = d; d += Lc;
+    S.c_lo = d; d += Lc; S.c_ro = d; d += Lc; S.c_lw = d; d += Lc; S.c_rw = d; d += Lc;
+    int* q = reinterpret_cast<int*>(d);
+    S.feat = q; q += Lc; S.node = q; q += Lc; S.rank = q; q += Lc; S.cfeat0 = q; q += Lc; S.cfeat1 = q; q += Lc;
+    S.cnode0 = q; q += Lc; S.cnode1 = q; q += Lc; S.lparent = q; q += Lc; S.ldepth = q; q += Lc; S.lcount = q; q += Lc;
+    S.c_leaf = q; q += Lc; S.c_node = q; q += Lc; S.c_lc = q; q += Lc; S.c_rc = q; q += Lc;
+    unsigned char* c = reinterpret_cast<unsigned char*>(q);
+    S.exp = c; c += Lc; S.isleft = c;
+  }
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int nl0 = ctrl->num_leaves;
+  // ---- P0
+  for (int i = tid; i < nl0; i += blockDim.x) {
     const int nd = avail[i];
-    s_node[i] = nd; s_gain[i] = nodes[nd].best.gain; s_feat[i] = nodes[nd].best.real_feature; s_exp[i] = nodes[nd].state == 1;
+    const NodeDev& N = nodes[nd];
+    S.node[i] = nd; S.gain[i] = N.best.gain; S.feat[i] = N.best.real_feature;
+    const bool e = N.state == 1;
+    S.exp[i] = e;
+    if (e) {
+      const int l = N.left, r = N.right;
+      S.cnode0[i] = l; S.cnode1[i] = r;
+      S.cgain0[i] = nodes[l].best.gain; S.cfeat0[i] = nodes[l].best.real_feature;
+      S.cgain1[i] = nodes[r].best.gain; S.cfeat1[i] = nodes[r].best.real_feature;
+    }
+    const int par = T.leaf_parent[i];
+    S.lparent[i] = par; S.ldepth[i] = T.leaf_depth[i]; S.lvalue[i] = T.leaf_value[i]; S.lweight[i] = T.leaf_weight[i];
+    S.lcount[i] = T.leaf_count[i];
+    S.isleft[i] = par >= 0 ? (T.left_child[par] == ~i) : 0;
   }
   __syncthreads();
-  // ---- replay the sequential order as far as the already expanded leaves allow
-  while (true) {
-    double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int i = tid; i < nl; i += blockDim.x) {
-      const double g = s_gain[i]; const int rf = s_feat[i];
-      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = i; }        // ascending i: the earlier leaf keeps ties
-    }
-    auto take = [&](double g, int rf, int i) {
-      if (i < 0) return;
-      if (bi < 0 || SplitBetter(g, rf, bg, bf) || (!SplitBetter(bg, bf, g, rf) && i < bi)) { bg = g; bf = rf; bi = i; }
-    };
-    for (int o = 16; o > 0; o >>= 1) {
-      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
-      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
-      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
-      take(g, rf, i);
-    }
-    if (lane == 0) { r_gain[warp] = bg; r_feat[warp] = bf; r_idx[warp] = bi; }
-    __syncthreads();
-    if (tid == 0) {
-      bg = r_gain[0]; bf = r_feat[0]; bi = r_idx[0];
-      for (int w = 1; w < 8; ++w) take(r_gain[w], r_feat[w], r_idx[w]);
-      s_best = bi;
-      if (nl >= L || !(bg > 0.0)) s_state = 1;
-      else if (!s_exp[bi]) s_state = 2;
-      else {
-        // ---- commit: Tree::Split with the leaf ids of the sequential learner (left keeps the id, right = num_leaves)
-        s_state = 0;
-        const int best_leaf = bi, nd = s_node[bi];
-        const NodeDev par = nodes[nd];
-        const SplitDev bs = par.best;
-        const int lnode = par.left, rnode = par.right;
-        const int lc = nodes[lnode].global_count, rc = nodes[rnode].global_count;
-        const int new_node = nl - 1, new_leaf = nl;
-        const FeatureMetaDev fm = fmeta[bs.feature];
-        const int parent = T.leaf_parent[best_leaf];
-        if (parent >= 0) {
-          if (T.left_child[parent] == ~best_leaf) T.left_child[parent] = new_node; else T.right_child[parent] = new_node;
-        }
-        T.split_feature_inner[new_node] = bs.feature;
-        T.split_gain[new_node] = static_cast<float>(bs.gain);
-        T.left_child[new_node] = ~best_leaf;
-        T.right_child[new_node] = ~new_leaf;
-        T.leaf_parent[best_leaf] = new_node;
-        T.leaf_parent[new_leaf] = new_node;
-        T.internal_weight[new_node] = bs.left_sum_h + bs.right_sum_h;
-        T.internal_value[new_node] = T.leaf_value[best_leaf];
-        T.internal_count[new_node] = lc + rc;
-        T.leaf_value[best_leaf] = (bs.left_output != bs.left_output) ? 0.0 : bs.left_output;
-        T.leaf_weight[best_leaf] = bs.left_sum_h;
-        T.leaf_count[best_leaf] = lc;
-        T.leaf_value[new_leaf] = (bs.right_output != bs.right_output) ? 0.0 : bs.right_output;
-        T.leaf_weight[new_leaf] = bs.right_sum_h;
-        T.leaf_count[new_leaf] = rc;
-        T.leaf_depth[new_leaf] = T.leaf_depth[best_leaf] + 1;
-        T.leaf_depth[best_leaf]++;
-        signed char dt = 0;
-        if (bs.default_left) dt |= 2;
-        dt |= static_cast<signed char>((fm.missing_type & 3) << 2);
-        T.decision_type[new_node] = dt;
-        T.threshold_in_bin[new_node] = bs.threshold;
-        nodes[nd].state = 2;
-        avail[best_leaf] = lnode; avail[new_leaf] = rnode;
-        s_node[best_leaf] = lnode; s_gain[best_leaf] = nodes[lnode].best.gain; s_feat[best_leaf] = nodes[lnode].best.real_feature;
-        s_exp[best_leaf] = nodes[lnode].state == 1;
-        s_node[new_leaf] = rnode; s_gain[new_leaf] = nodes[rnode].best.gain; s_feat[new_leaf] = nodes[rnode].best.real_feature;
-        s_exp[new_leaf] = nodes[rnode].state == 1;
+  // ---- P1: replay the sequential order as far as the already expanded leaves allow (warp 0)
+  if (tid < 32) {
+    int nl = nl0, m = 0, state = 0;
+    while (true) {
+      double bg = KMINSCORE; int bf = -1, bi = -1;
+      for (int i = lane; i < nl; i += 32) {
+        const double g = S.gain[i]; const int rf = S.feat[i];
+        if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = i; }        // ascending i: the earlier leaf keeps ties
       }
+      for (int o = 16; o > 0; o >>= 1) {
+        const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+        const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+        const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf) || (!SplitBetter(bg, bf, g, rf) && i < bi))) { bg = g; bf = rf; bi = i; }
+      }
+      if (nl >= L || !(bg > 0.0)) { state = 1; break; }
+      if (!S.exp[bi]) { state = 2; break; }
+      // commit: the left child keeps the leaf id, the right child becomes leaf `nl`
+      __syncwarp();
+      if (lane == 0) {
+        S.c_leaf[m] = bi; S.c_node[m] = S.node[bi];
+        const int l = S.cnode0[bi], r = S.cnode1[bi];
+        const double gl = S.cgain0[bi], gr = S.cgain1[bi];
+        const int fl = S.cfeat0[bi], fr = S.cfeat1[bi];
+        S.node[bi] = l; S.gain[bi] = gl; S.feat[bi] = fl; S.exp[bi] = 0;
+        S.node[nl] = r; S.gain[nl] = gr; S.feat[nl] = fr; S.exp[nl] = 0;
+      }
+      ++nl; ++m;
+      __syncwarp();
     }
-    __syncthreads();
-    if (s_state != 0) break;
-    ++nl;
-    __syncthreads();
+    if (lane == 0) { s_state = state; s_nl = nl; s_m = m; }
+  }
+  __syncthreads();
+  const int nl = s_nl, m = s_m;
+  // ---- P2: order-independent fields of every commit
+  for (int j = tid; j < m; j += blockDim.x) {
+    const int nd = S.c_node[j], best_leaf = S.c_leaf[j];
+    const int new_node = nl0 - 1 + j, new_leaf = nl0 + j;
+    const NodeDev& par = nodes[nd];
+    const int lnode = par.left, rnode = par.right;
+    const int feature = par.best.feature, threshold = par.best.threshold, default_left = par.best.default_left;
+    const double gain = par.best.gain, lo = par.best.left_output, ro = par.best.right_output;
+    const double lw = par.best.left_sum_h, rw = par.best.right_sum_h;
+    const int lc = nodes[lnode].global_count, rc = nodes[rnode].global_count;
+    const int missing_type = fmeta[feature].missing_type;
+    T.split_feature_inner[new_node] = feature;
+    T.split_gain[new_node] = static_cast<float>(gain);
+    T.left_child[new_node] = ~best_leaf;
+    T.right_child[new_node] = ~new_leaf;
+    T.internal_weight[new_node] = lw + rw;
+    T.internal_count[new_node] = lc + rc;
+    signed char dt = 0;
+    if (default_left) dt |= 2;
+    dt |= static_cast<signed char>((missing_type & 3) << 2);
+    T.decision_type[new_node] = dt;
+    T.threshold_in_bin[new_node] = threshold;
+    nodes[nd].state = 2;
+    S.c_lo[j] = (lo != lo) ? 0.0 : lo; S.c_ro[j] = (ro != ro) ? 0.0 : ro;
+    S.c_lw[j] = lw; S.c_rw[j] = rw; S.c_lc[j] = lc; S.c_rc[j] = rc;
+  }
+  __syncthreads();
+  // ---- P3: order-dependent bookkeeping
+  if (tid == 0) {
+    for (int j = 0; j < m; ++j) {
+      const int best_leaf = S.c_leaf[j], new_node = nl0 - 1 + j, new_leaf = nl0 + j;
+      const int parent = S.lparent[best_leaf];
+      if (parent >= 0) {
+        if (S.isleft[best_leaf]) T.left_child[parent] = new_node; else T.right_child[parent] = new_node;
+      }
+      T.internal_value[new_node] = S.lvalue[best_leaf];
+      S.lparent[best_leaf] = new_node; S.lparent[new_leaf] = new_node;
+      S.isleft[best_leaf] = 1; S.isleft[new_leaf] = 0;
+      S.lvalue[best_leaf] = S.c_lo[j]; S.lweight[best_leaf] = S.c_lw[j]; S.lcount[best_leaf] = S.c_lc[j];
+      S.lvalue[new_leaf] = S.c_ro[j]; S.lweight[new_leaf] = S.c_rw[j]; S.lcount[new_leaf] = S.c_rc[j];
+      S.ldepth[new_leaf] = S.ldepth[best_leaf] + 1;
+      S.ldepth[best_leaf] += 1;
+    }
+  }
+  __syncthreads();
+  // ---- P4: write the per-leaf arrays back
+  if (m > 0) {
+    for (int i = tid; i < nl; i += blockDim.x) {
+      T.leaf_parent[i] = S.lparent[i]; T.leaf_depth[i] = S.ldepth[i]; T.leaf_value[i] = S.lvalue[i];
+      T.leaf_weight[i] = S.lweight[i]; T.leaf_count[i] = S.lcount[i];
+      avail[i] = S.node[i];
+    }
   }
   if (s_state == 1) {
     if (tid == 0) { ctrl->done = 1; ctrl->num_leaves = nl; ctrl->batch_n = 0; }
@@ -501,14 +542,14 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   // ---- next batch: the best not-yet-expanded leaves whose rank is below the remaining leaf budget
   const int budget = L - nl;
   for (int i = tid; i < nl; i += blockDim.x) {
-    const double g = s_gain[i]; const int rf = s_feat[i];
+    const double g = S.gain[i]; const int rf = S.feat[i];
     int rank = 0;
     for (int j = 0; j < nl; ++j) {
       if (j == i) continue;
-      const double gj = s_gain[j]; const int fj = s_feat[j];
+      const double gj = S.gain[j]; const int fj = S.feat[j];
       rank += SplitBetter(gj, fj, g, rf) || (!SplitBetter(g, rf, gj, fj) && j < i);
     }
-    s_rank[i] = rank;
+    S.rank[i] = rank;
   }
   if (tid == 0) s_count = 0;
   __syncthreads();
@@ -519,21 +560,22 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   const int node_room = (max_nodes - ctrl->num_nodes) / 2;
   int kmax = min(min(max_batch, 1 + spec_left), node_room);
   if (kmax < 1) kmax = 1;
+  const int num_nodes = ctrl->num_nodes;
   for (int i = tid; i < nl; i += blockDim.x) {
-    const bool eligible = !s_exp[i] && s_gain[i] > 0.0 && s_rank[i] < budget;
+    const bool eligible = !S.exp[i] && S.gain[i] > 0.0 && S.rank[i] < budget;
     if (!eligible) continue;
     int pos = 0;
     for (int j = 0; j < nl; ++j)
-      if (j != i && !s_exp[j] && s_gain[j] > 0.0 && s_rank[j] < budget && s_rank[j] < s_rank[i]) ++pos;
+      if (j != i && !S.exp[j] && S.gain[j] > 0.0 && S.rank[j] < budget && S.rank[j] < S.rank[i]) ++pos;
     if (pos < kmax) {
       atomicAdd(&s_count, 1);
-      const int nd = s_node[i];
-      const NodeDev par = nodes[nd];
-      const SplitDev bs = par.best;
-      const FeatureMetaDev fm = fmeta[bs.feature];
+      const int nd = S.node[i];
+      const NodeDev& par = nodes[nd];
+      const int feature = par.best.feature;
+      const FeatureMetaDev fm = fmeta[feature];
       BatchItem it;
-      it.node = nd; it.left = ctrl->num_nodes + 2 * pos; it.right = it.left + 1;
-      it.feature = bs.feature; it.threshold = bs.threshold; it.default_left = bs.default_left;
+      it.node = nd; it.left = num_nodes + 2 * pos; it.right = it.left + 1;
+      it.feature = feature; it.threshold = par.best.threshold; it.default_left = par.best.default_left;
       it.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
       it.src_begin = par.begin; it.src_count = par.count; it.src_buf = par.buf;
       it.smaller = it.larger = -1; it.find = 0; it.parent_slot = par.hist_slot; it.pad_[0] = it.pad_[1] = 0;
@@ -544,11 +586,13 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   if (tid == 0) {
     const int bn = s_count;
     ctrl->batch_n = bn;
-    ctrl->num_nodes += 2 * bn;
+    ctrl->num_nodes = num_nodes + 2 * bn;
     ctrl->spec_used += bn - 1;      // statistics only
     ctrl->num_leaves = nl;
     ctrl->batch_rows = 0;
     ctrl->rounds += 1;
+    for (int k = 0; k < kMaxBatch; ++k) ctrl->part_cursor[k] = 0ULL;
+    ctrl->part_ctas_done = 0;
   }
 }
 

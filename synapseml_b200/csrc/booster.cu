@@ -100,12 +100,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     const char* env = getenv("LGB_B200_MAX_BATCH");
     max_batch_ = env ? std::max(1, std::min(kMaxBatch, atoi(env))) : kMaxBatch;
   }
+  if (const char* env = getenv("LGB_B200_PART_BLOCKS")) part_blocks_ = std::max(1, atoi(env));
   spec_budget_ = std::max(2 * kMaxBatch, (L - 1) / 2);
   const int max_expansions = (L - 1) + spec_budget_;
   max_nodes_ = 1 + 2 * max_expansions;
-  flag_stride_ = n_ / 32 + 2 * kPartThreads;
-  d_flags_.Alloc(static_cast<size_t>(flag_stride_) * kMaxBatch);
-  d_part_counts_.AllocZero(static_cast<size_t>(kPartBlocks) * kMaxBatch);
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
   d_hist_pool_.Alloc(hist_elems * (1 + max_expansions));
   d_hist_work_.Alloc(hist_elems * kMaxBatch);
@@ -133,6 +131,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
   }
+  SetSmem(k_bt_select, SelectSmemBytes(1024));   // the largest tree the learner accepts; launches ask for what their num_leaves needs
 #define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
@@ -374,22 +373,21 @@ void Booster::LaunchFind(bool root) {
 // and returns at once when the tree is finished, so rounds are enqueued without waiting for the GPU.
 void Booster::EnqueueRounds(int rounds) {
   for (int r = 0; r < rounds; ++r) {
-    ProfBegin("part_count");
-    LaunchPdl(k_bt_part_count, dim3(kPartBlocks, max_batch_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-              d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_, d_flags_.p, static_cast<long long>(flag_stride_), d_part_counts_.p);
-    ProfEnd();
-    ProfBegin("part_scatter");
-    LaunchPdl(k_bt_part_scatter, dim3(kPartBlocks, max_batch_), dim3(kPartThreads), 0, stream_, d_idx_[0].p, d_idx_[1].p, d_idx_[0].p,
-              d_idx_[1].p, idx_es_, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_flags_.p, static_cast<long long>(flag_stride_),
-              d_part_counts_.p, d_hist_work_.p, work_elems_, lp_);
+    ProfBegin("partition");
+    if (idx_es_ == 2)
+      LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_hist_work_.p, work_elems_, lp_);
+    else
+      LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_hist_work_.p, work_elems_, lp_);
     ProfEnd();
     ProfBegin("hist"); LaunchHist(false); ProfEnd();
     ProfBegin("find"); LaunchFind(false); ProfEnd();
     ProfBegin("select");
-    LaunchPdl(k_bt_select, dim3(1), dim3(256), 0, stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
+    LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
               spec_budget_, max_batch_);
     ProfEnd();
-    launches_ += 3;
+    launches_ += 2;
   }
 }
 
@@ -403,7 +401,7 @@ void Booster::TrainTree(HostTree* out) {
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
   ProfBegin("select");
-  LaunchPdl(k_bt_select, dim3(1), dim3(256), 0, stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
+  LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
             spec_budget_, max_batch_);
   ProfEnd();
   ++launches_;

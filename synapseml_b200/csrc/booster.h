@@ -114,8 +114,6 @@ class Booster {
   DevBuf<uint16_t> d_gh16_;          // quantized: (int8 grad << 8) | uint8 hess per row
   DevBuf<int2> d_ghfix_;             // float mode: fixed-point (grad, hess) per row
   DevBuf<int> d_idx_[2];
-  DevBuf<unsigned int> d_flags_;
-  DevBuf<int> d_part_counts_;
   DevBuf<long long> d_hist_pool_, d_hist_work_;
   NodeDev* d_nodes_ = nullptr;       // [max_nodes_]
   BatchCtrl* d_ctrl_ = nullptr;
@@ -139,8 +137,8 @@ class Booster {
   int64_t rounds_total_ = 0, expansions_total_ = 0, splits_total_ = 0;   // batched growth statistics over all trees
   double last_hist_ms_ = 0;
   int launches_ = 0;
-  long long flag_stride_ = 0;
   int work_elems_ = 0;
+  int part_blocks_ = 592;                   // 4 x 148 SMs (k_bt_partition is built for 4 CTAs per SM)
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;

@@ -494,18 +494,6 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   }
 }
 
-// ------------------------------------------------------------------------------------------------ K7 stable partition
-// A warp owns 32-row words of the leaf's index range: lanes are rows, one ballot gives the word's left/right flags.
-// pass 1 (count): flag word per 32 rows + per-block left counts.  pass 2 (scatter): block-local prefix over its words in
-// shared memory, then every warp writes its rows to the other index buffer with no further synchronisation; lefts and
-// rights each go to consecutive positions, so stores coalesce.  Order is preserved (the partition is stable).
-constexpr int kPartWordsPerIter = 2048;     // shared-memory prefix capacity (65536 rows) per block iteration
-
-__device__ __forceinline__ void PartChunk(int n, int* lo_w, int* hi_w) {
-  const int words = (n + 31) >> 5;
-  const int per = (words + gridDim.x - 1) / gridDim.x;
-  *lo_w = min(words, static_cast<int>(blockIdx.x) * per);
-  *hi_w = min(words, *lo_w + per);
-}
+// K7 (leaf partition) lives in batch_tree.cuh.
 
 }  // namespace lgb
