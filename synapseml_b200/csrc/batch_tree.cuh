@@ -59,7 +59,7 @@ struct BatchCtrl {
   int find_count[kMaxBatch][2];
   unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
   int part_ctas_done;                          // CTAs of the running partition kernel that are finished
-  int pad2_;
+  int applied;                                 // the finished tree has been added to the scores
   unsigned int max_abs_g_bits, max_abs_h_bits;
   double grad_scale, hess_scale, inv_grad_scale, inv_hess_scale;
   long long hist_rows, hist_launches;
@@ -84,7 +84,7 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
     nodes[0] = z;
     avail[0] = 0;
     ctrl->num_leaves = 1; ctrl->done = 0; ctrl->num_nodes = 1; ctrl->num_slots = 1; ctrl->batch_n = 0; ctrl->spec_used = 0;
-    ctrl->rounds = 0; ctrl->batch_rows = 0;
+    ctrl->rounds = 0; ctrl->batch_rows = 0; ctrl->applied = 0;
     for (int k = 0; k < kMaxBatch; ++k) { ctrl->find_count[k][0] = 0; ctrl->find_count[k][1] = 0; ctrl->part_cursor[k] = 0ULL; }
     ctrl->part_ctas_done = 0;
   }
@@ -596,51 +596,109 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   }
 }
 
-// ------------------------------------------------------------------------------------------------ K8 (batched learner)
-__global__ void __launch_bounds__(256) k_bt_sort_leaves(const NodeDev* __restrict__ nodes, const int* __restrict__ avail,
-                                                        const BatchCtrl* __restrict__ ctrl, int* __restrict__ sorted, int L) {
-  const int nl = ctrl->num_leaves;
-  for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-    const NodeDev& ni = nodes[avail[i]];
-    const int bi = ni.begin, ci = ni.count;
-    int rank = 0;
-    for (int j = 0; j < nl; ++j) {
-      const NodeDev& nj = nodes[avail[j]];
-      const int bj = nj.begin, cj = nj.count;
-      rank += (bj < bi) || (bj == bi && (cj < ci || (cj == ci && j < i)));
-    }
-    sorted[rank] = i;
-    sorted[L + rank] = bi;
-    sorted[2 * L + rank] = ni.buf;
+// ------------------------------------------------------------------------------------------------ K8 + K3 fused
+// Applies the finished tree to the training scores by walking it with every row's bins (row-major records, streamed once)
+// instead of going through the leaves' index ranges, and — for the row-wise objectives — computes the next iteration's
+// gradients and their max |g|, max |h| in the same pass (OBJ = 1 binary, 2 L2, 0 scores only).
+// The decisions are the partition kernel's: bin == nan_bin ? default_left : bin <= threshold.
+// A thread keeps its row's record in registers (WPR = 8 or 16 words; the bin is picked with selects, shared memory only
+// serves the 8-byte node table: one LDS per level); WPR = 0 reads the bins of wider records in place.
+constexpr int kApplyThreads = 256;
+constexpr int kApplyMaxFeatures = 1 << 14;      // node word: feature (14 bits) | nan bin (9) | threshold (8) | default_left (1)
+
+template <int WPR>
+__device__ __forceinline__ unsigned int PickBin(const unsigned int (&r)[WPR == 0 ? 1 : WPR], int f) {
+  const int w = f >> 2;
+  unsigned int v;
+  if (WPR == 8) {
+    const unsigned int t0 = (w & 1) ? r[1] : r[0], t1 = (w & 1) ? r[3] : r[2], t2 = (w & 1) ? r[5] : r[4], t3 = (w & 1) ? r[7] : r[6];
+    const unsigned int u0 = (w & 2) ? t1 : t0, u1 = (w & 2) ? t3 : t2;
+    v = (w & 4) ? u1 : u0;
+  } else {
+    unsigned int t[8];
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = (w & 1) ? r[(2 * i + 1) % (WPR == 0 ? 1 : WPR)] : r[(2 * i) % (WPR == 0 ? 1 : WPR)];
+    const unsigned int u0 = (w & 2) ? t[1] : t[0], u1 = (w & 2) ? t[3] : t[2], u2 = (w & 2) ? t[5] : t[4], u3 = (w & 2) ? t[7] : t[6];
+    const unsigned int x0 = (w & 4) ? u1 : u0, x1 = (w & 4) ? u3 : u2;
+    v = (w & 8) ? x1 : x0;
   }
+  return (v >> ((f & 3) * 8)) & 0xffu;
 }
 
-__global__ void __launch_bounds__(256) k_bt_score_update(double* __restrict__ score, const int* __restrict__ idx0,
-                                                         const int* __restrict__ idx1, int es, const BatchCtrl* __restrict__ ctrl,
-                                                         const int* __restrict__ sorted, int L, const double* __restrict__ leaf_value,
-                                                         double lr, int n) {
-  __shared__ int s_begin[1024], s_buf[1024];
+template <int OBJ, int WPR>
+__global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* __restrict__ rm, unsigned rm_stride,
+                                                                 double* __restrict__ score, const float* __restrict__ label,
+                                                                 const float* __restrict__ weight, float* __restrict__ grad,
+                                                                 float* __restrict__ hess, TreeArraysDev T,
+                                                                 const FeatureMetaDev* __restrict__ fmeta, BatchCtrl* __restrict__ ctrl,
+                                                                 double lr, int n, double sigmoid, double lw_neg, double lw_pos) {
   __shared__ double s_val[1024];
+  __shared__ uint2 s_node[1024];
   const int nl = ctrl->num_leaves;
-  if (nl <= 1) return;
+  if (!ctrl->done || ctrl->applied || nl <= 1) return;
   for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-    const int leaf = sorted[i];
-    s_begin[i] = sorted[L + i]; s_buf[i] = sorted[2 * L + i];
-    double v = leaf_value[leaf] * lr;
+    double v = T.leaf_value[i] * lr;
     const double zt = (double)1e-35f;
     if (v >= -zt && v <= zt) v = 0.0;
     s_val[i] = v;
+    if (i < nl - 1) {
+      const int f = T.split_feature_inner[i];
+      const int dt = T.decision_type[i];
+      const FeatureMetaDev fm = fmeta[f];
+      const unsigned nan_bin = (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1) : 256u;
+      uint2 nd;
+      nd.x = static_cast<unsigned>(f) | (nan_bin << 14) | (static_cast<unsigned>(T.threshold_in_bin[i]) << 23) | ((dt & 2) ? (1u << 31) : 0u);
+      nd.y = (static_cast<unsigned>(T.left_child[i]) & 0xffffu) | (static_cast<unsigned>(T.right_child[i]) << 16);
+      s_node[i] = nd;
+    }
   }
   __syncthreads();
-  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-    int lo = 0, hi = nl - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (s_begin[mid] <= p) lo = mid; else hi = mid - 1;
+  float mg = 0.0f, mh = 0.0f;
+  for (long long row = static_cast<long long>(blockIdx.x) * kApplyThreads + threadIdx.x; row < n;
+       row += static_cast<long long>(gridDim.x) * kApplyThreads) {
+    const uint8_t* rec = rm + static_cast<size_t>(row) * rm_stride;
+    unsigned int r[WPR == 0 ? 1 : WPR];
+    if (WPR != 0) {
+      #pragma unroll
+      for (int c = 0; c < WPR / 4; ++c) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(rec) + c);
+        r[4 * c] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+      }
     }
-    const int row = (s_buf[lo] == 0 ? idx0 : idx1)[static_cast<size_t>(p) * es];
-    score[row] += s_val[lo];
+    const double sc0 = score[row];
+    int node = 0;
+    do {
+      const uint2 nd = s_node[node];
+      const int f = nd.x & 0x3fffu;
+      const unsigned nan_bin = (nd.x >> 14) & 0x1ffu, thr = (nd.x >> 23) & 0xffu;
+      const unsigned bin = WPR != 0 ? PickBin<WPR>(r, f) : static_cast<unsigned>(__ldg(rec + f));
+      const bool left = (bin == nan_bin) ? ((nd.x >> 31) != 0) : (bin <= thr);
+      node = left ? static_cast<int>(static_cast<short>(nd.y & 0xffffu)) : static_cast<int>(static_cast<short>(nd.y >> 16));
+    } while (node >= 0);
+    const double sc = sc0 + s_val[~node];
+    score[row] = sc;
+    if (OBJ != 0) {
+      float g, h;
+      const bool has_w = weight != nullptr;
+      const float w = has_w ? weight[row] : 0.0f;
+      if (OBJ == 1) GradBinaryRow(sc, label[row], has_w, w, sigmoid, lw_neg, lw_pos, &g, &h);
+      else GradL2Row(sc, label[row], has_w, w, &g, &h);
+      grad[row] = g; hess[row] = h;
+      mg = fmaxf(mg, fabsf(g)); mh = fmaxf(mh, fabsf(h));
+    }
+  }
+  if (OBJ != 0) {
+    for (int o = 16; o > 0; o >>= 1) {
+      mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+      mh = fmaxf(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMax(&ctrl->max_abs_g_bits, __float_as_uint(mg));
+      atomicMax(&ctrl->max_abs_h_bits, __float_as_uint(mh));
+    }
   }
 }
+// marks the finished tree as applied (one thread, after k_bt_apply_tree): a second apply pass for the same tree does nothing
+__global__ void k_bt_mark_applied(BatchCtrl* ctrl) { if (ctrl->done) ctrl->applied = 1; }
 
 }  // namespace lgb

@@ -54,6 +54,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   LGB_CHECK(cfg_.tree_learner == "serial" || cfg_.tree_learner == "data" || cfg_.tree_learner == "data_parallel",
             "tree_learner=%s is not supported by this library (data_parallel / serial)", cfg_.tree_learner.c_str());
   LGB_CHECK(cfg_.num_leaves >= 2 && cfg_.num_leaves <= 1024, "num_leaves=%d is outside [2, 1024]", cfg_.num_leaves);
+  LGB_CHECK(train->num_features() <= kApplyMaxFeatures, "more than %d used features are not supported", kApplyMaxFeatures);
   LGB_CHECK(!cfg_.zero_as_missing, "zero_as_missing=true is not supported by this library yet");
   LGB_CHECK(cfg_.num_grad_quant_bins >= 2 && cfg_.num_grad_quant_bins <= 64, "num_grad_quant_bins=%d is outside [2, 64]", cfg_.num_grad_quant_bins);
   device_ = train->device;
@@ -90,7 +91,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   const int L = cfg_.num_leaves;
   d_score_.AllocZero(n_);
   if (train->has_init_score) LGB_CUDA(cudaMemcpy(d_score_.p, train->d_init_score.p, sizeof(double) * n_, cudaMemcpyDeviceToDevice));
-  d_grad_.Alloc(n_); d_hess_.Alloc(n_);
+  d_grad_[0].Alloc(n_); d_hess_[0].Alloc(n_); d_grad_[1].Alloc(n_); d_hess_[1].Alloc(n_);
+  if (const char* env = getenv("LGB_B200_FUSE_GRAD")) fuse_grad_ = atoi(env) != 0;
   if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
   idx_es_ = lp_.quantized ? 2 : 4;      // ints per index entry: {row, g|h} or {row, g, h, -}
   d_idx_[0].Alloc(n_ * idx_es_); d_idx_[1].Alloc(n_ * idx_es_);
@@ -114,7 +116,6 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   d_avail_.AllocZero(L);
   d_feat_best_.Alloc(static_cast<size_t>(2) * kMaxBatch * std::max(F_, 1));
   d_splittable_.Alloc(static_cast<size_t>(max_nodes_) * std::max(F_, 1));
-  d_sorted_leaf_.AllocZero(3 * L);
   // tree arrays blob: 8 int arrays [L], decision_type [L], split_gain [L], 4 double arrays [L]
   {
     const size_t ints = 8 * sizeof(int) * L, chars = RoundUp<size_t>(L, 8), floats = RoundUp<size_t>(sizeof(float) * L, 8), dbl = 4 * sizeof(double) * L;
@@ -272,14 +273,14 @@ void Booster::ComputeGradients() {
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
   const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
   if (obj_ == kBinary) {
-    k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_.p, d_hess_.p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
+    k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
-    k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_.p, d_hess_.p, n);
+    k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
   } else {
     LambdarankArgs a;
     a.score = d_score_.p; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
     a.inv_max_dcg = d_inv_max_dcg_.p; a.label_gain = d_label_gain_.p; a.discount = d_discount_.p; a.sigmoid_table = d_sigmoid_table_.p;
-    a.grad = d_grad_.p; a.hess = d_hess_.p; a.sigmoid = cfg_.sigmoid; a.min_sigmoid_input = min_sigmoid_input_;
+    a.grad = d_grad_[grad_cur_].p; a.hess = d_hess_[grad_cur_].p; a.sigmoid = cfg_.sigmoid; a.min_sigmoid_input = min_sigmoid_input_;
     a.max_sigmoid_input = max_sigmoid_input_; a.idx_factor = sigmoid_table_idx_factor_;
     a.truncation_level = cfg_.lambdarank_truncation_level; a.norm = cfg_.lambdarank_norm; a.table_size = 1024 * 1024;
     a.max_cnt = max_query_len_;
@@ -293,14 +294,16 @@ void Booster::ComputeGradients() {
   ++launches_;
 }
 
-void Booster::PrepareGradients() {
+void Booster::PrepareGradients(bool absmax_ready) {
   const int n = static_cast<int>(n_);
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
-  k_absmax<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, d_ctrl_);
+  if (!absmax_ready) {
+    LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
+    k_absmax<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, d_ctrl_);
+  }
   if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
   k_scales<<<1, 1, 0, stream_>>>(d_ctrl_, lp_);
-  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_.p, d_hess_.p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
+  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
                                         static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p);
   LGB_CUDA(cudaGetLastError());
   launches_ += 3;
@@ -458,14 +461,32 @@ bool Booster::FetchTree(HostTree* t) {
   return true;
 }
 
+// Adds the finished tree to the training scores.  For the row-wise objectives the same pass also produces the gradients of
+// the next iteration (into the other gradient buffer) and their absolute maxima, which the next UpdateOneIter then picks up
+// instead of running the gradient and max kernels; if no further iteration follows, they are simply never used.
 void Booster::UpdateScores() {
-  const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
-  k_bt_sort_leaves<<<1, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_sorted_leaf_.p, L);
-  k_bt_score_update<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, d_idx_[0].p, d_idx_[1].p, idx_es_, d_ctrl_,
-                                                                                d_sorted_leaf_.p, L, tree_dev_.leaf_value,
-                                                                                cfg_.learning_rate, n);
+  const BinLayout& lay = ds_->layout;
+  const int obj = (fuse_grad_ && obj_ == kBinary) ? 1 : (fuse_grad_ && obj_ == kL2) ? 2 : 0;
+  const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
+  const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
+  float* g = d_grad_[grad_cur_ ^ 1].p;
+  float* h = d_hess_[grad_cur_ ^ 1].p;
+  if (obj != 0) LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
+#define APPLY_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_score_.p, ds_->d_label.p, w, g, h, tree_dev_, ds_->d_fmeta.p, d_ctrl_, \
+                   cfg_.learning_rate, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]
+#define APPLY(OBJ)                                                                                              \
+  do {                                                                                                          \
+    if (lay.rm_stride == 32) k_bt_apply_tree<OBJ, 8><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);          \
+    else if (lay.rm_stride == 64) k_bt_apply_tree<OBJ, 16><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);    \
+    else k_bt_apply_tree<OBJ, 0><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);                              \
+  } while (0)
+  if (obj == 1) APPLY(1); else if (obj == 2) APPLY(2); else APPLY(0);
+#undef APPLY
+#undef APPLY_ARGS
+  k_bt_mark_applied<<<1, 1, 0, stream_>>>(d_ctrl_);
   LGB_CUDA(cudaGetLastError());
+  grad_ready_ = obj != 0;
   launches_ += 2;
 }
 
@@ -503,8 +524,11 @@ bool Booster::UpdateOneIter() {
   tree.num_leaves = 1;
   tree.leaf_value.assign(1, 0.0);
   if (need_train_ && F_ > 0) {
-    ProfBegin("gradients"); ComputeGradients(); ProfEnd();
-    ProfBegin("quantize"); PrepareGradients(); ProfEnd();
+    const bool fused = grad_ready_;       // produced by the previous iteration's apply-tree pass
+    if (fused) grad_cur_ ^= 1;
+    else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
+    grad_ready_ = false;
+    ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
     TrainTree(&tree);
   }
   bool should_continue = false;
@@ -578,8 +602,8 @@ void Booster::CopyScores(double* out) const {
 void Booster::CopyGradients(float* g, float* h) const {
   LGB_CUDA(cudaSetDevice(device_));
   Sync();
-  LGB_CUDA(cudaMemcpy(g, d_grad_.p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
-  LGB_CUDA(cudaMemcpy(h, d_hess_.p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(g, d_grad_[grad_cur_].p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(h, d_hess_[grad_cur_].p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
 }
 
 void Booster::CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const {

@@ -110,7 +110,12 @@ class Booster {
 
   // device state
   DevBuf<double> d_score_;
-  DevBuf<float> d_grad_, d_hess_;
+  // two gradient buffers: the fused apply-tree kernel writes the NEXT iteration's gradients while [grad_cur_] still holds the
+  // ones the finished iteration trained on
+  DevBuf<float> d_grad_[2], d_hess_[2];
+  int grad_cur_ = 0;
+  bool grad_ready_ = false;     // [grad_cur_ ^ 1] and the control block's max |g|, max |h| are valid for the next iteration
+  bool fuse_grad_ = true;
   DevBuf<uint16_t> d_gh16_;          // quantized: (int8 grad << 8) | uint8 hess per row
   DevBuf<int2> d_ghfix_;             // float mode: fixed-point (grad, hess) per row
   DevBuf<int> d_idx_[2];
@@ -125,7 +130,6 @@ class Booster {
   TreeArraysDev tree_dev_{};
   size_t tree_blob_bytes_ = 0;
   std::vector<unsigned char> h_tree_blob_;
-  DevBuf<int> d_sorted_leaf_;        // [num_leaves] begin-sorted leaf ids + [num_leaves] begins
   // lambdarank
   DevBuf<double> d_sigmoid_table_, d_inv_max_dcg_, d_label_gain_, d_discount_;
   double min_sigmoid_input_ = -50, max_sigmoid_input_ = 50, sigmoid_table_idx_factor_ = 1;
@@ -154,7 +158,7 @@ class Booster {
   void InitObjective();
   double BoostFromScoreLocalSums(double* suml, double* sumw) const;
   void ComputeGradients();
-  void PrepareGradients();           // absmax -> scales -> quantize / fixed point
+  void PrepareGradients(bool absmax_ready);           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
   void LaunchFind(bool root);

@@ -31,35 +31,43 @@ __device__ __forceinline__ int RoundIntD(double x) { return static_cast<int>(x +
 __device__ __forceinline__ int SignD(double x) { return (x > 0.0) - (x < 0.0); }
 
 // ------------------------------------------------------------------------------------------------ K3 gradients
+// Row-wise objectives as device functions: the stand-alone gradient kernels and the fused apply-tree kernel (batch_tree.cuh)
+// must produce the same bits.
+__device__ __forceinline__ void GradBinaryRow(double score, float label, bool has_w, float w, double sigmoid, double lw_neg,
+                                              double lw_pos, float* g, float* h) {
+  const int is_pos = label > 0.0f;
+  const int lab = is_pos ? 1 : -1;
+  const double lw = is_pos ? lw_pos : lw_neg;
+  const double response = -lab * sigmoid / (1.0f + SoftExp(lab * sigmoid * score));
+  const double abs_response = fabs(response);
+  if (!has_w) {
+    *g = static_cast<float>(response * lw);
+    *h = static_cast<float>(abs_response * (sigmoid - abs_response) * lw);
+  } else {
+    *g = static_cast<float>(response * lw * w);
+    *h = static_cast<float>(abs_response * (sigmoid - abs_response) * lw * w);
+  }
+}
+__device__ __forceinline__ void GradL2Row(double score, float label, bool has_w, float w, float* g, float* h) {
+  if (!has_w) {
+    *g = static_cast<float>(score - label);
+    *h = 1.0f;
+  } else {
+    *g = static_cast<float>(static_cast<float>(score - label) * w);
+    *h = static_cast<float>(w);
+  }
+}
+
 __global__ void k_grad_binary(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
                               float* __restrict__ grad, float* __restrict__ hess, int n, double sigmoid, double lw_neg, double lw_pos) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int is_pos = label[i] > 0.0f;
-    const int lab = is_pos ? 1 : -1;
-    const double lw = is_pos ? lw_pos : lw_neg;
-    const double response = -lab * sigmoid / (1.0f + SoftExp(lab * sigmoid * score[i]));
-    const double abs_response = fabs(response);
-    if (weight == nullptr) {
-      grad[i] = static_cast<float>(response * lw);
-      hess[i] = static_cast<float>(abs_response * (sigmoid - abs_response) * lw);
-    } else {
-      grad[i] = static_cast<float>(response * lw * weight[i]);
-      hess[i] = static_cast<float>(abs_response * (sigmoid - abs_response) * lw * weight[i]);
-    }
-  }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    GradBinaryRow(score[i], label[i], weight != nullptr, weight ? weight[i] : 0.0f, sigmoid, lw_neg, lw_pos, grad + i, hess + i);
 }
 
 __global__ void k_grad_l2(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
                           float* __restrict__ grad, float* __restrict__ hess, int n) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    if (weight == nullptr) {
-      grad[i] = static_cast<float>(score[i] - label[i]);
-      hess[i] = 1.0f;
-    } else {
-      grad[i] = static_cast<float>(static_cast<float>(score[i] - label[i]) * weight[i]);
-      hess[i] = static_cast<float>(weight[i]);
-    }
-  }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    GradL2Row(score[i], label[i], weight != nullptr, weight ? weight[i] : 0.0f, grad + i, hess + i);
 }
 
 // LambdaRank-NDCG.  One CTA per query.  Step 1: stable rank of every document by score (descending) by counting, which
