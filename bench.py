@@ -220,14 +220,23 @@ def main():
     root_rows = n_local * args.steps
     nonroot_rows = max(hist_rows - root_rows, 0)
     hist_launches = s1["hist_launches"] - s0["hist_launches"]
+    hist_kernel_launches = max(s1["hist_kernel_launches"] - s0["hist_kernel_launches"], 1)
     bytes_alg = root_rows * (N_FEAT + 2) + nonroot_rows * (N_FEAT + 2 + 4) + hist_launches * N_FEAT * 256 * 16
     peak, peak_src = measured_peak()
     achieved = bytes_alg / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
     root_ms = C.c_float()
     validate(lightgbmlib().LGBM_B200_BoosterTimeRootHistogram(booster.booster_handle, 5, C.byref(root_ms)))
     root_gbs = n_local * (N_FEAT + 2) / (root_ms.value * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_hist (histogram construction, K4)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    traffic, traffic_src = None, None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_hist_traffic.json")
+    if os.path.exists(tpath):       # DRAM bytes per launch from the committed ncu --set full capture of the same workload
+        tj = json.load(open(tpath))
+        traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+    roofline = {"bound": "hbm", "kernel": "k_bt_hist (histogram construction, K4)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes_per_launch": bytes_alg / hist_kernel_launches,
+                "avg_launch_us": hist_ms * 1e3 / hist_kernel_launches, "kernel_launches_per_step": hist_kernel_launches / args.steps,
+                "peak_source": peak_src,
                 "frac_of_spec_8000": achieved / 8000.0,
                 "algorithmic_bytes": "per row visit: 28 bin bytes + 2 (int8 g,h) + 4 row index (0 at the root); + F*256*16 output per launch",
                 "hist_ms_per_step": hist_ms / args.steps, "hist_share_of_step": hist_ms / ms_timed_pass,

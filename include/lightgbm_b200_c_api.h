@@ -135,7 +135,8 @@ int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable);
 int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches,
                               int64_t* hist_launches);
 /* batched best-first growth statistics summed over all trees: dependent rounds, leaves expanded, splits kept */
-int LGBM_B200_BoosterGetGrowthStats(BoosterHandle handle, int64_t* rounds, int64_t* expansions, int64_t* splits);
+int LGBM_B200_BoosterGetGrowthStats(BoosterHandle handle, int64_t* rounds, int64_t* expansions, int64_t* splits,
+                                    int64_t* hist_kernel_launches);
 /* the TCP hand-off LGBM_NetworkInit uses for the NCCL unique id (CPU-only; for tests of the multi-process path) */
 int LGBM_B200_NetworkBootstrapBlob(const char* machines, int local_listen_port, int listen_time_out, uint8_t* blob, int32_t bytes,
                                    int* out_rank);

@@ -356,6 +356,7 @@ void Booster::LaunchHist(bool root) {
   LGB_CUDA(cudaGetLastError());
   if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
   ++launches_;
+  ++hist_kernel_launches_;
   // data-parallel learner: every rank needs the global histograms of the batch (integer sums: order-independent)
   if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, static_cast<size_t>(work_elems_) * (root ? 1 : max_batch_), stream_);
 }

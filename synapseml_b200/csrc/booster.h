@@ -87,6 +87,7 @@ class Booster {
   int64_t growth_rounds() const { return rounds_total_; }
   int64_t growth_expansions() const { return expansions_total_; }
   int64_t growth_splits() const { return splits_total_; }
+  int64_t hist_kernel_launches() const { return hist_kernel_launches_; }
   double last_hist_ms() const { return last_hist_ms_; }
   int launches() const { return launches_; }
   void EnableHistTiming(bool on) { time_hist_ = on; }
@@ -138,7 +139,7 @@ class Booster {
   // measurement
   bool time_hist_ = false;
   int64_t last_rows_visited_ = 0, hist_launches_ = 0;
-  int64_t rounds_total_ = 0, expansions_total_ = 0, splits_total_ = 0;   // batched growth statistics over all trees
+  int64_t rounds_total_ = 0, expansions_total_ = 0, splits_total_ = 0, hist_kernel_launches_ = 0;   // batched growth statistics over all trees
   double last_hist_ms_ = 0;
   int launches_ = 0;
   int work_elems_ = 0;

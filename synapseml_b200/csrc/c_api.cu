@@ -323,11 +323,14 @@ int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, 
   API_END();
 }
 // Batched best-first growth, summed over all trees so far: rounds = dependent expand rounds, expansions = leaves expanded
-// (partition + histogram + split search), splits = expansions that ended up in a tree.
-int LGBM_B200_BoosterGetGrowthStats(BoosterHandle handle, int64_t* rounds, int64_t* expansions, int64_t* splits) {
+// (partition + histogram + split search), splits = expansions that ended up in a tree, hist_kernel_launches = launches of the
+// histogram kernel (a launch covers every leaf of a round; rounds enqueued past the end of a tree return at once).
+int LGBM_B200_BoosterGetGrowthStats(BoosterHandle handle, int64_t* rounds, int64_t* expansions, int64_t* splits,
+                                    int64_t* hist_kernel_launches) {
   API_BEGIN();
   auto b = static_cast<Booster*>(handle);
   *rounds = b->growth_rounds(); *expansions = b->growth_expansions(); *splits = b->growth_splits();
+  *hist_kernel_launches = b->hist_kernel_launches();
   API_END();
 }
 // TCP hand-off used by LGBM_NetworkInit to distribute the NCCL unique id, exposed so the multi-process path can be tested

@@ -63,10 +63,10 @@ class LightGBMBooster:
     def stats(self):
         rows, ms, launches, hl = C.c_int64(), C.c_double(), C.c_int64(), C.c_int64()
         validate(lightgbmlib().LGBM_B200_BoosterGetStats(self.booster_handle, C.byref(rows), C.byref(ms), C.byref(launches), C.byref(hl)), "stats")
-        r, e, sp = C.c_int64(), C.c_int64(), C.c_int64()
-        validate(lightgbmlib().LGBM_B200_BoosterGetGrowthStats(self.booster_handle, C.byref(r), C.byref(e), C.byref(sp)), "stats")
+        r, e, sp, hk = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        validate(lightgbmlib().LGBM_B200_BoosterGetGrowthStats(self.booster_handle, C.byref(r), C.byref(e), C.byref(sp), C.byref(hk)), "stats")
         return dict(hist_rows_visited=rows.value, hist_ms=ms.value, kernel_launches=launches.value, hist_launches=hl.value,
-                    growth_rounds=r.value, growth_expansions=e.value, growth_splits=sp.value)
+                    growth_rounds=r.value, growth_expansions=e.value, growth_splits=sp.value, hist_kernel_launches=hk.value)
 
     def timer_start(self):
         validate(lightgbmlib().LGBM_B200_BoosterTimerStart(self.booster_handle), "timer")
