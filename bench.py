@@ -252,7 +252,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         est2 = estimator(args.steps)
-        df = LocalDataFrame([{"features": X, "label": y}])
+        df = LocalDataFrame.from_arrays(X, y, num_partitions=8)     # 8 task threads push concurrently, as 8 Spark tasks would
         barrier()
         t0 = time.time()
         model = est2.fit(df)
@@ -265,6 +265,8 @@ def main():
         h2d = X.nbytes + y.nbytes + (BIN_SAMPLE * N_FEAT * 8 if rank == 0 else 0)
         e2e = {"value": N * args.steps / dt, "unit": "rows*iters/s", "h2d_bytes_per_step": h2d / args.steps,
                "d2h_bytes_per_step": len(model.model_str) / args.steps, "seconds": dt,
+               "phases_seconds": {k: round(float(v), 4) for k, v in (est2.performance_measures or {}).items()
+                                  if k.endswith("Time")},
                "includes": "bin-boundary search on the 200k-row sample, H2D of the f64 rows (pinned staging), row binning, "
                            "%d boosting iterations, model string read-back" % args.steps}
     if rank != 0:

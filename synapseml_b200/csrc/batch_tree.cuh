@@ -137,8 +137,8 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;
   const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
   __syncthreads();
-  HistRows<R, BPL, FLT, ROOT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
-                              work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
+  HistRows<R, BPL, FLT, ROOT, !FLT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
+                                    work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6
@@ -172,7 +172,14 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
   const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
   const NodeDev& Nd = nodes[node];
-  longlong2 v = *reinterpret_cast<const longlong2*>(work + static_cast<size_t>(root ? 0 : k) * work_elems + off);
+  longlong2 v;
+  if (QUANT) {     // packed work area: (sum g << 32) + sum h
+    const long long pk = work[static_cast<size_t>(root ? 0 : k) * work_elems + static_cast<size_t>(f) * kBins + b];
+    v.y = pk & 0xffffffffLL;
+    v.x = (pk - v.y) >> 32;
+  } else {
+    v = *reinterpret_cast<const longlong2*>(work + static_cast<size_t>(root ? 0 : k) * work_elems + off);
+  }
   bool used = true;
   if (!root) {
     used = splittable[static_cast<size_t>(parent) * F + f] != 0;

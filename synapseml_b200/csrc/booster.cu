@@ -109,7 +109,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
   d_hist_pool_.Alloc(hist_elems * (1 + max_expansions));
   d_hist_work_.Alloc(hist_elems * kMaxBatch);
-  work_elems_ = static_cast<int>(hist_elems);
+  // quantized mode packs (sum g, sum h) of a bin into one int64 (hist_kernel.cuh), float mode keeps two
+  work_elems_ = static_cast<int>(lp_.quantized ? hist_elems / 2 : hist_elems);
+  LGB_CHECK(!lp_.quantized || static_cast<double>(n_global_) * cfg_.num_grad_quant_bins < 4294967296.0,
+            "use_quantized_grad: num_data * num_grad_quant_bins must stay below 2^32");
   LGB_CUDA(cudaMalloc(&d_nodes_, sizeof(NodeDev) * max_nodes_));
   LGB_CUDA(cudaMalloc(&d_ctrl_, sizeof(BatchCtrl)));
   LGB_CUDA(cudaMemset(d_ctrl_, 0, sizeof(BatchCtrl)));
@@ -634,7 +637,18 @@ void Booster::DebugRootHistogram(long long* out) {
                                                                   static_cast<int>(n_), static_cast<int>(n_global_));
   LaunchHist(true);
   Sync();
-  LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
+  // out: [F][256][2] (sum g, sum h); the quantized work area is packed, one int64 per bin
+  if (lp_.quantized) {
+    std::vector<long long> pk(work_elems_);
+    LGB_CUDA(cudaMemcpy(pk.data(), d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < work_elems_; ++i) {
+      const long long h = pk[i] & 0xffffffffLL;
+      out[2 * i] = (pk[i] - h) >> 32;
+      out[2 * i + 1] = h;
+    }
+  } else {
+    LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
+  }
 }
 
 void Booster::TimerStart() {

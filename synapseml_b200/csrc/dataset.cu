@@ -9,6 +9,8 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <map>
+#include <mutex>
 
 namespace lgb {
 
@@ -168,13 +170,21 @@ __device__ int K1ValueToBin(double value, const double* bounds, int num_bin, int
   return l;
 }
 
-// sorted: every feature's segment sorted ascending, NaNs last.  distinct/counts: scratch with room for n_f + 2 per feature
-// (offset seg_off[f] + 2 f).  bounds/tmp/upper/lower/cib: [F][bstride].
-__global__ void k1_find_bin(const double* sorted, const long long* seg_off, const int* na_cnt_arr, int nfeat, K1Params p,
-                            double* distinct, int* counts, double* bounds, double* tmp, double* upper, double* lower,
-                            int* cib, K1Meta* meta) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+// sorted: every feature's segment sorted ascending, NaNs last.  distinct/counts/starts: scratch with room for n_f + 2 per
+// feature (offset seg_off[f] + 2 f).  bounds/tmp/upper/lower/cib: [F][bstride].
+// One CTA per feature.  The O(n_sample) part — runs of (ulp-)equal values -> distinct values + counts, with the implicit
+// zero entry inserted where the sorted values cross zero — is done by the whole CTA (flag, block scan with carry, gather);
+// the greedy bin construction is inherently sequential over the distinct values and runs on thread 0 with register
+// accumulators (no read-modify-write of global memory inside its loops).
+constexpr int kK1Threads = 256;
+__global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, const long long* seg_off, const int* na_cnt_arr, int nfeat,
+                                                        K1Params p, double* distinct, int* counts, int* starts, double* bounds, double* tmp,
+                                                        double* upper, double* lower, int* cib, K1Meta* meta) {
+  const int f = blockIdx.x;
   if (f >= nfeat) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ int s_warp[kK1Threads / 32];
+  __shared__ int s_carry, s_nd;
   const double* v = sorted + seg_off[f];
   const int n_all = (int)(seg_off[f + 1] - seg_off[f]);
   int na_cnt = na_cnt_arr[f];
@@ -188,20 +198,57 @@ __global__ void k1_find_bin(const double* sorted, const long long* seg_off, cons
   const int zero_cnt = p.total_sample_cnt - nv - na_cnt;
   double* dv = distinct + seg_off[f] + 2LL * f;
   int* dc = counts + seg_off[f] + 2LL * f;
-  int nd = 0;
-  if (nv == 0 || (v[0] > 0.0 && zero_cnt > 0)) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
-  if (nv > 0) { dv[nd] = v[0]; dc[nd] = 1; ++nd; }
-  for (int i = 1; i < nv; ++i) {
-    const double a = v[i - 1], b = v[i];
-    if (!EqualOrdered(a, b)) {
-      if (a < 0.0 && b > 0.0) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
-      dv[nd] = b; dc[nd] = 1; ++nd;
-    } else {
-      dv[nd - 1] = b;
-      ++dc[nd - 1];
+  int* st = starts + seg_off[f] + 2LL * f;
+  // ---- pass 1: entry index of every run start; st[g] = first position of the run (a zero entry gets -1)
+  const bool lead_zero = nv == 0 || (v[0] > 0.0 && zero_cnt > 0);
+  if (tid == 0) { s_carry = lead_zero ? 1 : 0; if (lead_zero) st[0] = -1; }
+  __syncthreads();
+  for (int c0 = 0; c0 < nv; c0 += kK1Threads) {
+    const int i = c0 + tid;
+    bool start = false, cross = false;
+    if (i < nv) {
+      if (i == 0) start = true;
+      else {
+        const double a = v[i - 1], b = v[i];
+        start = !EqualOrdered(a, b);
+        cross = start && a < 0.0 && b > 0.0;
+      }
     }
+    const int inc = (start ? 1 : 0) + (cross ? 1 : 0);
+    int incl = inc;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < kK1Threads / 32; ++w) { if (w < warp) before += s_warp[w]; total += s_warp[w]; }
+    const int carry = s_carry;
+    if (start) {
+      const int g = carry + before + incl - 1;
+      st[g] = i;
+      if (cross) st[g - 1] = -1;
+    }
+    __syncthreads();
+    if (tid == 0) s_carry = carry + total;
+    __syncthreads();
   }
-  if (nv > 0 && v[nv - 1] < 0.0 && zero_cnt > 0) { dv[nd] = 0.0; dc[nd] = zero_cnt; ++nd; }
+  if (tid == 0) {
+    int nd = s_carry;
+    if (nv > 0 && v[nv - 1] < 0.0 && zero_cnt > 0) { st[nd] = -1; ++nd; }
+    s_nd = nd;
+  }
+  __syncthreads();
+  const int nd = s_nd;
+  // ---- pass 2: a run's value is its last element (what the sequential sweep leaves behind), its count the run length
+  for (int g = tid; g < nd; g += kK1Threads) {
+    const int b0 = st[g];
+    if (b0 < 0) { dv[g] = 0.0; dc[g] = zero_cnt; continue; }
+    int e = nv;
+    for (int h = g + 1; h < nd; ++h) { const int t = st[h]; if (t >= 0) { e = t; break; } }     // at most one zero entry in between
+    dv[g] = v[e - 1];
+    dc[g] = e - b0;
+  }
+  __syncthreads();
+  if (tid != 0) return;
   K1Meta m;
   m.min_val = dv[0];
   m.max_val = dv[nd - 1];
@@ -222,11 +269,18 @@ __global__ void k1_find_bin(const double* sorted, const long long* seg_off, cons
   int* c = cib + (long long)f * p.bstride;
   for (int i = 0; i < num_bin; ++i) c[i] = 0;
   {
-    int i_bin = 0;
+    int i_bin = 0, acc = 0;
+    double bound = out[0];
     for (int i = 0; i < nd; ++i) {
-      while (dv[i] > out[i_bin] && i_bin < num_bin - 1) ++i_bin;
-      c[i_bin] += dc[i];
+      const double x = dv[i];
+      if (x > bound && i_bin < num_bin - 1) {
+        c[i_bin] = acc; acc = 0;
+        while (x > out[i_bin] && i_bin < num_bin - 1) ++i_bin;
+        bound = out[i_bin];
+      }
+      acc += dc[i];
     }
+    c[i_bin] = acc;
     if (missing_type == kMissingNaN) c[num_bin - 1] = na_cnt;
   }
   int is_trivial = num_bin <= 1;
@@ -440,7 +494,7 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   const long long total = off[ncol];
   DevBuf<double> d_vals, d_sorted, d_distinct, d_bnd, d_tmp, d_up, d_lo;
   DevBuf<long long> d_off;
-  DevBuf<int> d_na, d_counts, d_cib;
+  DevBuf<int> d_na, d_counts, d_starts, d_cib;
   DevBuf<K1Meta> d_meta;
   d_vals.Alloc(std::max<long long>(total, 1));
   d_sorted.Alloc(std::max<long long>(total, 1));
@@ -473,11 +527,12 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   p.bstride = c.max_bin + 4;
   d_distinct.Alloc(total + 2LL * ncol + 2);
   d_counts.Alloc(total + 2LL * ncol + 2);
+  d_starts.Alloc(total + 2LL * ncol + 2);
   const size_t bs = static_cast<size_t>(ncol) * p.bstride;
   d_bnd.Alloc(bs); d_tmp.Alloc(bs); d_up.Alloc(bs); d_lo.Alloc(bs); d_cib.Alloc(bs);
   d_meta.Alloc(ncol);
-  k1_find_bin<<<CeilDiv(ncol, 32), 32>>>(d_sorted.p, d_off.p, d_na.p, ncol, p, d_distinct.p, d_counts.p, d_bnd.p, d_tmp.p,
-                                         d_up.p, d_lo.p, d_cib.p, d_meta.p);
+  k1_find_bin<<<ncol, kK1Threads>>>(d_sorted.p, d_off.p, d_na.p, ncol, p, d_distinct.p, d_counts.p, d_starts.p, d_bnd.p, d_tmp.p,
+                                    d_up.p, d_lo.p, d_cib.p, d_meta.p);
   LGB_CUDA(cudaGetLastError());
   LGB_CUDA(cudaDeviceSynchronize());
   std::vector<K1Meta> hmeta(ncol);
@@ -574,7 +629,36 @@ void Dataset::SetFeatureNames(const char** names, int n) {
   feature_names.assign(names, names + n);
 }
 
-constexpr size_t kStageBytes = size_t(32) << 20;
+constexpr size_t kStageBytes = size_t(8) << 20;
+
+// Page-locked staging buffers are expensive to create (tens of milliseconds per 64 MB), so they are kept for the life of the
+// process and handed from one dataset to the next (a fit creates a dataset per executor; repeated fits reuse the buffers).
+namespace {
+struct PinnedCache {
+  std::mutex mu;
+  std::multimap<size_t, void*> free_list;
+  size_t cached_bytes = 0;
+  static constexpr size_t kMaxCached = size_t(1) << 30;
+  void* Get(size_t bytes) {
+    {
+      std::lock_guard<std::mutex> g(mu);
+      auto it = free_list.find(bytes);
+      if (it != free_list.end()) { void* p = it->second; free_list.erase(it); cached_bytes -= bytes; return p; }
+    }
+    void* p = nullptr;
+    LGB_CUDA(cudaMallocHost(&p, bytes));
+    return p;
+  }
+  void Put(void* p, size_t bytes) {
+    {
+      std::lock_guard<std::mutex> g(mu);
+      if (cached_bytes + bytes <= kMaxCached) { free_list.emplace(bytes, p); cached_bytes += bytes; return; }
+    }
+    cudaFreeHost(p);
+  }
+};
+PinnedCache& Pinned() { static PinnedCache* c = new PinnedCache(); return *c; }   // never destroyed: outlives the CUDA context teardown order
+}  // namespace
 
 void Dataset::EnsureSlots(int n) {
   std::lock_guard<std::mutex> g(mu_);
@@ -584,7 +668,8 @@ void Dataset::EnsureSlots(int n) {
     s.cap_rows = std::max<size_t>(kStageBytes / (sizeof(double) * num_total_features), 1);
     const size_t bytes = s.cap_rows * num_total_features * sizeof(double);
     for (int k = 0; k < 2; ++k) {
-      LGB_CUDA(cudaMallocHost(&s.pinned[k], bytes));
+      s.pinned[k] = static_cast<double*>(Pinned().Get(bytes));
+      s.pinned_bytes = bytes;
       LGB_CUDA(cudaMalloc(&s.dstage[k], bytes));
       LGB_CUDA(cudaEventCreateWithFlags(&s.ev[k], cudaEventDisableTiming));
     }
@@ -598,7 +683,7 @@ void Dataset::FreeSlots() {
   for (auto& s : slots_) {
     if (s.stream) cudaStreamSynchronize(s.stream);
     for (int k = 0; k < 2; ++k) {
-      if (s.pinned[k]) cudaFreeHost(s.pinned[k]);
+      if (s.pinned[k]) Pinned().Put(s.pinned[k], s.pinned_bytes);
       if (s.dstage[k]) cudaFree(s.dstage[k]);
       if (s.ev[k]) cudaEventDestroy(s.ev[k]);
     }

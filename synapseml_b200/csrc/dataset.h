@@ -114,6 +114,7 @@ class Dataset {
     cudaEvent_t ev[2] = {nullptr, nullptr};
     cudaStream_t stream = nullptr;
     size_t cap_rows = 0;
+    size_t pinned_bytes = 0;
     int cur = 0;
     int64_t seg_start = 0;
     int64_t seg_rows = 0;

@@ -61,7 +61,9 @@ __device__ __forceinline__ void HistUpdate(unsigned bins, unsigned lane_addr, un
 // Accumulates rows [lo, hi) of a leaf (positions into its index range; ROOT: positions are row ids) into the CTA's shared
 // histograms and flushes them into the global int64 histogram `work` (every rows_per_flush rows and at the end).  The shared
 // arrays must be zero on entry and are zero again on return.  Shared by k_hist and the persistent tree kernel.
-template <int R, int BPL, bool FLT, bool ROOT>
+// PACK (quantized mode only): `work` holds ONE int64 per (feature, bin), (sum g << 32) + sum h — valid while the global sum of
+// h stays below 2^32 — so a flush is one global atomic per bin instead of two.
+template <int R, int BPL, bool FLT, bool ROOT, bool PACK = false>
 __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride, const uint16_t* __restrict__ gh16,
                                          const int2* __restrict__ ghfix, const int* idx, int begin, int lo, int hi,
                                          unsigned lane_addr, unsigned int* hsm, long long* work, int F, int tile,
@@ -206,9 +208,14 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
         }
       }
       if (f < F && (g != 0 || h != 0)) {
-        unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
-        if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
-        if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
+        if (PACK) {
+          atomicAdd(reinterpret_cast<unsigned long long*>(work + static_cast<size_t>(f) * kBins + bin),
+                    static_cast<unsigned long long>(g * 4294967296LL + h));
+        } else {
+          unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
+          if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
+          if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
+        }
       }
     }
     __syncthreads();

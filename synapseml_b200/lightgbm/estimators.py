@@ -135,20 +135,30 @@ class LightGBMBase:
         num_samples = min(bin_sample_count, total_num_rows)
         mode = g["samplingMode"]
         feats = [p["features"] for p in df.partitions if len(p["label"])]
+
+        def head(k):      # df.limit(k) without materialising the whole frame
+            out, need = [], k
+            for f in feats:
+                if need <= 0:
+                    break
+                out.append(f[:need])
+                need -= len(out[-1])
+            return out[0] if len(out) == 1 else np.concatenate(out)
+
         if mode == "fixed":       # df.limit(numSamples)
-            return np.concatenate(feats)[:num_samples]
+            return head(num_samples)
         seed = g["dataRandomSeed"] if g["dataRandomSeed"] is not None else 0
         fraction = 1.0 if total_num_rows < bin_sample_count else min(1.0, (bin_sample_count + 10000.0) / total_num_rows)
         rng = np.random.Generator(np.random.PCG64(seed))
-        allx = np.concatenate(feats)
         if mode == "global":      # sample(fraction, seed).limit(numSamples)
+            allx = np.concatenate(feats)
             keep = rng.random(len(allx)) < fraction
             return allx[keep][:num_samples]
         # "subset" (default): limit(samplingSubsetSize).sample(fraction, seed), with samplingSubsetSize capped at numSamples (:733)
         subset = min(g["samplingSubsetSize"], num_samples)
-        head = allx[:subset]
-        keep = rng.random(len(head)) < fraction
-        return head[keep]
+        hd = head(subset)
+        keep = rng.random(len(hd)) < fraction
+        return hd[keep]
 
     def preprocess_data(self, df):
         return df
@@ -183,7 +193,10 @@ class LightGBMBase:
             ds_params = g["passThroughArgs"] + " " + ds_params
         measures = {}
         ctx = dict(train_params=train_params, dataset_params=ds_params, num_cols=num_cols, feature_names=g["slotNames"],
-                   measures=measures, hist_timing=getattr(self, "_hist_timing", False), keep_scores=getattr(self, "_keep_scores", False))
+                   measures=measures, hist_timing=getattr(self, "_hist_timing", False), keep_scores=getattr(self, "_keep_scores", False),
+                   # one pushing thread per partition, as Spark runs one task thread per partition on an executor
+                   # (BasePartitionTask.scala:84-112); the native push is thread-safe for distinct tid
+                   threaded_push=getattr(self, "_threaded_push", True))
         if g["dataTransferMode"] == "streaming":
             serialized = g["referenceDataset"]
             if serialized is None:

@@ -10,6 +10,7 @@ One executor == one process == one GPU.  `partitions` is the list of this execut
 """
 import ctypes as C
 import threading
+import time
 
 import numpy as np
 
@@ -32,7 +33,9 @@ class BasePartitionTask:
         ctx = self.ctx
         partitions = [p for p in partitions if len(p["label"]) > 0]      # empty partitions short-circuit (:134-136)
         measures = ctx.setdefault("measures", {})
+        t0 = time.time()
         dataset = self.prepare_dataset(partitions)
+        measures["datasetCreationTime"] = time.time() - t0      # LightGBMPerformance.scala: the executor's dataset phase
         info = ctx.get("network_info")
         if info is not None:
             nm.init_lightgbm_network(info)
@@ -41,13 +44,17 @@ class BasePartitionTask:
             dataset.validate_dataset()
             if ctx.get("feature_names"):
                 dataset.set_feature_names(ctx["feature_names"], ctx["num_cols"])
+            t0 = time.time()
             booster = train_utils.create_booster(ctx["train_params"], dataset)
+            measures["boosterCreationTime"] = time.time() - t0
             if ctx.get("hist_timing"):
                 booster.set_hist_timing(True)
             train_utils.execute_training_iterations(ctx["train_params"], booster, measures)
             measures.update(booster.stats())
             # only the main worker of rank 0 returns the model (BasePartitionTask.getPartitionTaskResult :450-461)
+            t0 = time.time()
             model_str = booster.save_to_string() if (info is None or info.rank == 0) else None
+            measures["saveModelTime"] = time.time() - t0
             if ctx.get("keep_scores"):
                 measures["train_scores"] = booster.inner_predict(0)
             return model_str
