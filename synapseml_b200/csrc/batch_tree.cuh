@@ -91,7 +91,10 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
 }
 
 // ------------------------------------------------------------------------------------------------ K4 wrapper
-// grid = (row CTAs, feature tiles, batch slots).  The row CTAs of a round are shared out over the batch by row count.
+// grid = (row CTAs, feature tiles).  ROOT: the CTAs share the rows of node 0.  Otherwise the smaller children of the round are
+// cut into chunks of rows_per_cta rows, sized so that there are at most as many chunks as row CTAs; CTA x takes chunk x.  (One
+// CTA fits per SM — 160 KB of shared memory — so a grid with a CTA per (chunk, batch slot) would run in several waves of
+// mostly idle CTAs; that was 15 us of fixed cost per round.)
 template <int R, int BPL, bool FLT, bool ROOT>
 __global__ void __launch_bounds__(kHistThreads, 1)
 k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
@@ -103,7 +106,7 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   PdlLaunchDependents();
   const int lane = threadIdx.x & 31;
   const int q = lane % LPR;
-  const int tile = blockIdx.y, k = blockIdx.z;
+  const int tile = blockIdx.y;
   const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
   const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
   unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
@@ -111,34 +114,57 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   const bool kmask = (tile * FT + q * BPL) < F;
   const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + (kmask ? q : 0) * BPL;
   asm volatile("" : "+l"(rmc));
+  __shared__ int s_node[kMaxBatch], s_chunks[kMaxBatch + 1];
+  __shared__ int s_rpc;
   PdlWait();
   if (ctrl->done) return;
-  int node;
-  long long total_rows;
-  if (ROOT) { node = 0; total_rows = nodes[0].count; }
-  else {
-    if (k >= ctrl->batch_n || !ctrl->batch[k].find) return;
-    node = ctrl->batch[k].smaller;
-    total_rows = ctrl->batch_rows;
+  if (threadIdx.x == 0) {
+    const int bn = ROOT ? 1 : ctrl->batch_n;
+    long long total = 0;
+    int active = 0;
+    for (int k = 0; k < kMaxBatch; ++k) {
+      int nd = -1;
+      if (ROOT) { if (k == 0) nd = 0; }
+      else if (k < bn && ctrl->batch[k].find) nd = ctrl->batch[k].smaller;
+      s_node[k] = nd;
+      if (nd >= 0) { total += nodes[nd].count; ++active; }
+    }
+    const int avail_ctas = max(1, row_ctas - active);
+    long long rpc = (total + avail_ctas - 1) / avail_ctas;
+    int rows_per_cta = static_cast<int>(rpc > 0x3fffffff ? 0x3fffffff : rpc);
+    rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
+    s_rpc = rows_per_cta;
+    int c = 0;
+    for (int k = 0; k < kMaxBatch; ++k) {
+      s_chunks[k] = c;
+      if (s_node[k] >= 0) {
+        const int cnt = nodes[s_node[k]].count;
+        c += (cnt + rows_per_cta - 1) / rows_per_cta;
+        if (blockIdx.x == 0 && tile == 0) {
+          atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(cnt));
+          atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
+        }
+      }
+    }
+    s_chunks[kMaxBatch] = c;
   }
-  const NodeDev& nd = nodes[node];
-  const int begin = nd.begin, count = nd.count, buf = nd.buf;
-  if (blockIdx.x == 0 && tile == 0 && threadIdx.x == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(count));
-    atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
-  }
-  long long rpc = (total_rows + row_ctas - 1) / row_ctas;
-  int rows_per_cta = static_cast<int>(rpc > 0x3fffffff ? 0x3fffffff : rpc);
-  rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
-  const long long lo_ll = static_cast<long long>(blockIdx.x) * rows_per_cta;
-  if (lo_ll >= count) return;
-  const int lo = static_cast<int>(lo_ll);
-  const int hi = min(count, lo + rows_per_cta);
-  for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;
-  const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
   __syncthreads();
-  HistRows<R, BPL, FLT, ROOT, !FLT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
-                                    work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
+  const int total_chunks = s_chunks[kMaxBatch];
+  if (static_cast<int>(blockIdx.x) >= total_chunks) return;
+  const int rows_per_cta = s_rpc;
+  for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;
+  __syncthreads();
+  for (int chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {      // normally one chunk per CTA
+    int k = 0;
+    while (k + 1 < kMaxBatch && chunk >= s_chunks[k + 1]) ++k;
+    const NodeDev& nd = nodes[s_node[k]];
+    const int begin = nd.begin, count = nd.count, buf = nd.buf;
+    const int lo = (chunk - s_chunks[k]) * rows_per_cta;
+    const int hi = min(count, lo + rows_per_cta);
+    const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
+    HistRows<R, BPL, FLT, ROOT, !FLT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
+                                      work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6

@@ -320,7 +320,7 @@ void Booster::LaunchHist(bool root) {
   const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
   const int tiles = CeilDiv(F_, ft);
   const int row_ctas = std::max(1, kNumSms / tiles);
-  dim3 grid(row_ctas, tiles, root ? 1 : max_batch_);
+  dim3 grid(row_ctas, tiles);
   int rows_per_flush;
   if (flt) {
     rows_per_flush = kFixRowsPerCopy * R;
