@@ -95,29 +95,22 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
 // cut into chunks of rows_per_cta rows, sized so that there are at most as many chunks as row CTAs; CTA x takes chunk x.  (One
 // CTA fits per SM — 160 KB of shared memory — so a grid with a CTA per (chunk, batch slot) would run in several waves of
 // mostly idle CTAs; that was 15 us of fixed cost per round.)
+// The body: all kHistThreads threads of a CTA; (cta_x, tile) = the CTA's place in a (row_ctas x tiles) arrangement.  The shared
+// histograms must be zero on entry and are zero again on return.
+struct HistShared { int node[kMaxBatch]; int chunks[kMaxBatch + 1]; int rpc; };
+
 template <int R, int BPL, bool FLT, bool ROOT>
-__global__ void __launch_bounds__(kHistThreads, 1)
-k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-          const int* __restrict__ idx0, const int* __restrict__ idx1, const NodeDev* __restrict__ nodes,
-          BatchCtrl* __restrict__ ctrl, long long* __restrict__ work, int work_elems, int F, int rows_per_flush, int row_ctas) {
-  extern __shared__ unsigned int hsm_raw[];
+__device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16,
+                                         const int2* __restrict__ ghfix, const int* idx0, const int* idx1, const NodeDev* nodes,
+                                         BatchCtrl* ctrl, long long* work, int work_elems, int F, int rows_per_flush, int row_ctas,
+                                         int cta_x, int tile, unsigned int* hsm, unsigned lane_addr, HistShared* sh) {
   constexpr int LPR = 32 / R;
   constexpr int FT = LPR * BPL;
-  PdlLaunchDependents();
   const int lane = threadIdx.x & 31;
   const int q = lane % LPR;
-  const int tile = blockIdx.y;
-  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
-  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
-  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
-  const unsigned lane_addr = sbase + lane * 4;
   const bool kmask = (tile * FT + q * BPL) < F;
   const uint8_t* rmc = rm + static_cast<size_t>(tile) * FT + (kmask ? q : 0) * BPL;
   asm volatile("" : "+l"(rmc));
-  __shared__ int s_node[kMaxBatch], s_chunks[kMaxBatch + 1];
-  __shared__ int s_rpc;
-  PdlWait();
-  if (ctrl->done) return;
   if (threadIdx.x == 0) {
     const int bn = ROOT ? 1 : ctrl->batch_n;
     long long total = 0;
@@ -126,68 +119,84 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
       int nd = -1;
       if (ROOT) { if (k == 0) nd = 0; }
       else if (k < bn && ctrl->batch[k].find) nd = ctrl->batch[k].smaller;
-      s_node[k] = nd;
+      sh->node[k] = nd;
       if (nd >= 0) { total += nodes[nd].count; ++active; }
     }
     const int avail_ctas = max(1, row_ctas - active);
     long long rpc = (total + avail_ctas - 1) / avail_ctas;
     int rows_per_cta = static_cast<int>(rpc > 0x3fffffff ? 0x3fffffff : rpc);
     rows_per_cta = max((rows_per_cta + 31) & ~31, kHistMinRowsPerCta);
-    s_rpc = rows_per_cta;
+    sh->rpc = rows_per_cta;
     int c = 0;
     for (int k = 0; k < kMaxBatch; ++k) {
-      s_chunks[k] = c;
-      if (s_node[k] >= 0) {
-        const int cnt = nodes[s_node[k]].count;
+      sh->chunks[k] = c;
+      if (sh->node[k] >= 0) {
+        const int cnt = nodes[sh->node[k]].count;
         c += (cnt + rows_per_cta - 1) / rows_per_cta;
-        if (blockIdx.x == 0 && tile == 0) {
+        if (cta_x == 0 && tile == 0) {
           atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(cnt));
           atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
         }
       }
     }
-    s_chunks[kMaxBatch] = c;
+    sh->chunks[kMaxBatch] = c;
   }
   __syncthreads();
-  const int total_chunks = s_chunks[kMaxBatch];
-  if (static_cast<int>(blockIdx.x) >= total_chunks) return;
-  const int rows_per_cta = s_rpc;
-  for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;
-  __syncthreads();
-  for (int chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {      // normally one chunk per CTA
+  const int total_chunks = sh->chunks[kMaxBatch];
+  const int rows_per_cta = sh->rpc;
+  for (int chunk = cta_x; chunk < total_chunks; chunk += row_ctas) {      // normally one chunk per CTA
     int k = 0;
-    while (k + 1 < kMaxBatch && chunk >= s_chunks[k + 1]) ++k;
-    const NodeDev& nd = nodes[s_node[k]];
+    while (k + 1 < kMaxBatch && chunk >= sh->chunks[k + 1]) ++k;
+    const NodeDev& nd = nodes[sh->node[k]];
     const int begin = nd.begin, count = nd.count, buf = nd.buf;
-    const int lo = (chunk - s_chunks[k]) * rows_per_cta;
+    const int lo = (chunk - sh->chunks[k]) * rows_per_cta;
     const int hi = min(count, lo + rows_per_cta);
     const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
     HistRows<R, BPL, FLT, ROOT, !FLT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
                                       work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
   }
+  __syncthreads();      // sh is rewritten by the next call
+}
+
+template <int R, int BPL, bool FLT, bool ROOT>
+__global__ void __launch_bounds__(kHistThreads, 1)
+k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+          const int* __restrict__ idx0, const int* __restrict__ idx1, const NodeDev* __restrict__ nodes,
+          BatchCtrl* __restrict__ ctrl, long long* __restrict__ work, int work_elems, int F, int rows_per_flush, int row_ctas) {
+  extern __shared__ unsigned int hsm_raw[];
+  __shared__ HistShared sh;
+  PdlLaunchDependents();
+  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
+  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
+  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
+  const unsigned lane_addr = sbase + (threadIdx.x & 31) * 4;
+  for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;      // before the wait: overlaps the predecessor
+  PdlWait();
+  if (ctrl->done) return;
+  __syncthreads();
+  HistBody<R, BPL, FLT, ROOT>(rm, rm_stride, gh16, ghfix, idx0, idx1, nodes, ctrl, work, work_elems, F, rows_per_flush, row_ctas,
+                              blockIdx.x, blockIdx.y, hsm, lane_addr, &sh);
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6
 // grid = (F, root ? 1 : 2, batch slots).  CTA (f, c, k): child c of batch item k (c = 0: the freshly built smaller child,
 // c = 1: the larger child = parent - smaller).  The last CTA of each (k, c) reduces the per-feature results to the child's
 // best split.
+// One unit = (feature f, child c, batch slot k), run by a 256-thread sub-block (named barriers, so several can share a CTA).
 template <bool QUANT>
-__global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
-                                                 const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
-                                                 BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
-                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root) {
-  PdlLaunchDependents();
-  PdlWait();
-  if (ctrl->done) return;
-  __shared__ int s_last;
-  __shared__ double s_gain[8];
-  __shared__ int s_feat[8], s_idx[8];
+__device__ __forceinline__ void FindUnit(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
+                                         NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
+                                         const LearnerParams& P, int root, int f, int c, int k, int sub) {
+  __shared__ int s_last_all[kMaxFindSubs];
+  __shared__ double s_gain_all[kMaxFindSubs][8];
+  __shared__ int s_feat_all[kMaxFindSubs][8], s_idx_all[kMaxFindSubs][8];
+  int& s_last = s_last_all[sub];
+  double* s_gain = s_gain_all[sub]; int* s_feat = s_feat_all[sub]; int* s_idx = s_idx_all[sub];
   const int F = P.num_features;
-  const int f = blockIdx.x, c = blockIdx.y, k = blockIdx.z, b = threadIdx.x;
+  const int b = threadIdx.x & (kFindThreads - 1);
   int node, parent = -1, parent_slot = 0;
   if (root) node = 0;
   else {
-    if (k >= ctrl->batch_n || !ctrl->batch[k].find) return;
     const BatchItem& it = ctrl->batch[k];
     node = c == 0 ? it.smaller : it.larger;
     parent = it.node;
@@ -222,39 +231,54 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   } else {
     long long tg, th;
     BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, Nd.int_g, Nd.int_h, Nd.sum_g, Nd.sum_h, Nd.global_count, P, gscale, hscale,
-                         fb + f, spl, &tg, &th, 0);
+                         fb + f, spl, &tg, &th, sub);
     if (root && f == 0 && b == 0) {
       nodes[0].int_g = tg; nodes[0].int_h = th;
       nodes[0].sum_g = static_cast<double>(tg) * gscale; nodes[0].sum_h = static_cast<double>(th) * hscale;
     }
   }
   __threadfence();
-  __syncthreads();
+  SubSync(sub);
   if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == F - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  double bg = KMINSCORE; int bf = -1, bi = -1;
-  for (int j = b; j < F; j += blockDim.x) {
-    const double g = fb[j].gain; const int rf = fb[j].real_feature;
-    if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+  SubSync(sub);
+  if (s_last) {       // the last unit of this child reduces over the features
+    __threadfence();
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int j = b; j < F; j += kFindThreads) {
+      const double g = fb[j].gain; const int rf = fb[j].real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+    }
+    const int lane = b & 31, warp = b >> 5;
+    for (int o = 16; o > 0; o >>= 1) {
+      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
+    }
+    if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
+    SubSync(sub);
+    if (b == 0) {
+      bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
+      for (int w = 1; w < 8; ++w)
+        if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
+      nodes[node].best = fb[bi];
+      ctrl->find_count[root ? 0 : k][c] = 0;
+    }
   }
-  const int lane = b & 31, warp = b >> 5;
-  for (int o = 16; o > 0; o >>= 1) {
-    const double g = __shfl_xor_sync(0xffffffffu, bg, o);
-    const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
-    const int i = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
-  }
-  if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
-  __syncthreads();
-  if (b == 0) {
-    bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
-    for (int w = 1; w < 8; ++w)
-      if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
-    nodes[node].best = fb[bi];
-    ctrl->find_count[root ? 0 : k][c] = 0;
-  }
+  SubSync(sub);       // the sub-block's shared scratch is reused by its next unit
+}
+
+template <bool QUANT>
+__global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
+                                                 const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
+                                                 BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
+                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root) {
+  PdlLaunchDependents();
+  PdlWait();
+  if (ctrl->done) return;
+  const int k = blockIdx.z;
+  if (!root && (k >= ctrl->batch_n || !ctrl->batch[k].find)) return;
+  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, blockIdx.x, blockIdx.y, k, 0);
 }
 
 // ------------------------------------------------------------------------------------------------ K7 (batched, one pass)
@@ -305,40 +329,34 @@ __device__ __forceinline__ void PublishChildren(BatchCtrl* ctrl, NodeDev* nodes,
   if (find) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->batch_rows), static_cast<unsigned long long>(left_smaller ? nl_true : nr_true));
 }
 
+// Tile list of the round (one thread): tiles[k] = first tile of batch item k, tiles[kMaxBatch] = total.
+__device__ __forceinline__ void PartTileList(const BatchCtrl* ctrl, int bn, int* tiles) {
+  int t = 0;
+  for (int k = 0; k < kMaxBatch; ++k) {
+    tiles[k] = t;
+    if (k < bn) t += max(1, (ctrl->batch[k].src_count + kPartTileRows - 1) / kPartTileRows);
+  }
+  tiles[kMaxBatch] = t;
+}
+
+// Tiles vb, vb + nvb, ... by one 256-thread sub-block (named barriers: several sub-blocks can share a CTA).
+// A tile is a chain of three dependent memory round trips (entries -> bins -> cursor atomic) before its stores; what hides
+// them is the number of tiles in flight per SM (8192 rows), not anything inside one sub-block.
 template <int ES>
-__global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t* __restrict__ cm, long long n_pad,
-                                                               const int* __restrict__ idx0r, const int* __restrict__ idx1r,
-                                                               int* __restrict__ idx0w, int* __restrict__ idx1w,
-                                                               const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-                                                               BatchCtrl* __restrict__ ctrl, NodeDev* __restrict__ nodes,
-                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
-  PdlLaunchDependents();
-  PdlWait();
-  if (ctrl->done) return;
-  const int bn = ctrl->batch_n;
+__device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, long long n_pad, const int* idx0r, const int* idx1r,
+                                               int* idx0w, int* idx1w, const uint16_t* __restrict__ gh16,
+                                               const int2* __restrict__ ghfix, BatchCtrl* ctrl, int bn, const int* s_tiles, int vb,
+                                               int nvb, int sub) {
   constexpr int NW = kPartThreads / 32;
   constexpr int WPW = kPartTileWords / NW;      // words per warp
-  __shared__ int s_tiles[kMaxBatch + 1];
-  __shared__ int s_wl[NW], s_wv[NW];
-  __shared__ unsigned long long s_base;
-  __shared__ int s_lastcta;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  // the histograms of this batch accumulate into work[0..bn) with atomics: clear them here
-  for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < static_cast<size_t>(bn) * work_elems; i += static_cast<size_t>(gridDim.x) * blockDim.x)
-    work[i] = 0;
-  if (threadIdx.x == 0) {
-    int t = 0;
-    for (int k = 0; k < kMaxBatch; ++k) {
-      s_tiles[k] = t;
-      if (k < bn) t += max(1, (ctrl->batch[k].src_count + kPartTileRows - 1) / kPartTileRows);
-    }
-    s_tiles[kMaxBatch] = t;
-  }
-  __syncthreads();
+  __shared__ int s_wl_all[kMaxFindSubs][NW], s_wv_all[kMaxFindSubs][NW];
+  __shared__ unsigned long long s_base_all[kMaxFindSubs];
+  int* s_wl = s_wl_all[sub]; int* s_wv = s_wv_all[sub];
+  unsigned long long& s_base = s_base_all[sub];
+  const int t = threadIdx.x & (kPartThreads - 1);
+  const int lane = t & 31, warp = t >> 5;
   const int total_tiles = s_tiles[kMaxBatch];
-  // A tile is a chain of three dependent memory round trips (entries -> bins -> cursor atomic) before its stores; what hides
-  // them is the number of tiles in flight per SM (4 CTAs of 8 rows per thread: 8192 rows), not anything inside one CTA.
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+  for (int tile = vb; tile < total_tiles; tile += nvb) {
     int k = 0;
     while (k + 1 < bn && tile >= s_tiles[k + 1]) ++k;
     const BatchItem& it = ctrl->batch[k];
@@ -381,7 +399,7 @@ __global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t*
       wl += __popc(lmask[u]); wr += __popc(rmask[u]);
     }
     if (lane == 0) { s_wl[warp] = wl; s_wv[warp] = wr; }
-    __syncthreads();
+    SubSync(sub);
     int lefts_before = 0, rights_before = 0, tile_l = 0, tile_r = 0;
     #pragma unroll
     for (int w = 0; w < NW; ++w) {
@@ -389,9 +407,9 @@ __global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t*
       if (w < warp) { lefts_before += a; rights_before += v; }
       tile_l += a; tile_r += v;
     }
-    if (threadIdx.x == 0)
+    if (t == 0)
       s_base = atomicAdd(&ctrl->part_cursor[k], (static_cast<unsigned long long>(tile_l) << 32) | static_cast<unsigned>(tile_r));
-    __syncthreads();
+    SubSync(sub);
     const unsigned long long base = s_base;
     const int lbase = static_cast<int>(base >> 32), rbase = static_cast<int>(base & 0xffffffffu);
     // lefts of this tile: [begin + lbase, +tile_l); rights: [begin + n - rbase - tile_r, begin + n - rbase)
@@ -410,6 +428,27 @@ __global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t*
       rpos += __popc(rmask[u]);
     }
   }
+}
+
+template <int ES>
+__global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t* __restrict__ cm, long long n_pad,
+                                                               const int* __restrict__ idx0r, const int* __restrict__ idx1r,
+                                                               int* __restrict__ idx0w, int* __restrict__ idx1w,
+                                                               const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
+                                                               BatchCtrl* __restrict__ ctrl, NodeDev* __restrict__ nodes,
+                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
+  PdlLaunchDependents();
+  PdlWait();
+  if (ctrl->done) return;
+  const int bn = ctrl->batch_n;
+  __shared__ int s_tiles[kMaxBatch + 1];
+  __shared__ int s_lastcta;
+  // the histograms of this batch accumulate into work[0..bn) with atomics: clear them here
+  for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < static_cast<size_t>(bn) * work_elems; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    work[i] = 0;
+  if (threadIdx.x == 0) PartTileList(ctrl, bn, s_tiles);
+  __syncthreads();
+  PartitionTiles<ES>(cm, n_pad, idx0r, idx1r, idx0w, idx1w, gh16, ghfix, ctrl, bn, s_tiles, blockIdx.x, gridDim.x, 0);
   // the CTA that finishes last publishes the children of the whole batch
   __threadfence();
   __syncthreads();
@@ -438,13 +477,10 @@ struct SelectSmem {
 constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 14 * sizeof(int) + 2;
 __host__ __device__ inline size_t SelectSmemBytes(int L) { return kSelectSmemPerLeaf * static_cast<size_t>((L + 7) & ~7) + 64; }
 
-__global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, int* __restrict__ avail, BatchCtrl* __restrict__ ctrl,
-                                                   TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
-                                                   int max_nodes, int spec_budget, int max_batch) {
-  PdlLaunchDependents();
-  PdlWait();
-  if (ctrl->done) return;
-  extern __shared__ double sel_smem_raw[];
+// The body: 256 threads (threadIdx.x < 256 of one CTA), synchronised with the named barrier of sub-block 0.
+__device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl* ctrl, const TreeArraysDev& T,
+                                           const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P, int max_nodes,
+                                           int spec_budget, int max_batch, double* sel_smem_raw) {
   __shared__ int s_state, s_nl, s_m, s_count;
   const int L = P.num_leaves;
   const int Lc = (L + 7) & ~7;
@@ -463,7 +499,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   const int tid = threadIdx.x, lane = tid & 31;
   const int nl0 = ctrl->num_leaves;
   // ---- P0
-  for (int i = tid; i < nl0; i += blockDim.x) {
+  for (int i = tid; i < nl0; i += kFindThreads) {
     const int nd = avail[i];
     const NodeDev& N = nodes[nd];
     S.node[i] = nd; S.gain[i] = N.best.gain; S.feat[i] = N.best.real_feature;
@@ -480,7 +516,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
     S.lcount[i] = T.leaf_count[i];
     S.isleft[i] = par >= 0 ? (T.left_child[par] == ~i) : 0;
   }
-  __syncthreads();
+  SubSync(0);
   // ---- P1: replay the sequential order as far as the already expanded leaves allow (warp 0)
   if (tid < 32) {
     int nl = nl0, m = 0, state = 0;
@@ -513,10 +549,10 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
     }
     if (lane == 0) { s_state = state; s_nl = nl; s_m = m; }
   }
-  __syncthreads();
+  SubSync(0);
   const int nl = s_nl, m = s_m;
   // ---- P2: order-independent fields of every commit
-  for (int j = tid; j < m; j += blockDim.x) {
+  for (int j = tid; j < m; j += kFindThreads) {
     const int nd = S.c_node[j], best_leaf = S.c_leaf[j];
     const int new_node = nl0 - 1 + j, new_leaf = nl0 + j;
     const NodeDev& par = nodes[nd];
@@ -541,7 +577,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
     S.c_lo[j] = (lo != lo) ? 0.0 : lo; S.c_ro[j] = (ro != ro) ? 0.0 : ro;
     S.c_lw[j] = lw; S.c_rw[j] = rw; S.c_lc[j] = lc; S.c_rc[j] = rc;
   }
-  __syncthreads();
+  SubSync(0);
   // ---- P3: order-dependent bookkeeping
   if (tid == 0) {
     for (int j = 0; j < m; ++j) {
@@ -559,10 +595,10 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
       S.ldepth[best_leaf] += 1;
     }
   }
-  __syncthreads();
+  SubSync(0);
   // ---- P4: write the per-leaf arrays back
   if (m > 0) {
-    for (int i = tid; i < nl; i += blockDim.x) {
+    for (int i = tid; i < nl; i += kFindThreads) {
       T.leaf_parent[i] = S.lparent[i]; T.leaf_depth[i] = S.ldepth[i]; T.leaf_value[i] = S.lvalue[i];
       T.leaf_weight[i] = S.lweight[i]; T.leaf_count[i] = S.lcount[i];
       avail[i] = S.node[i];
@@ -574,7 +610,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   }
   // ---- next batch: the best not-yet-expanded leaves whose rank is below the remaining leaf budget
   const int budget = L - nl;
-  for (int i = tid; i < nl; i += blockDim.x) {
+  for (int i = tid; i < nl; i += kFindThreads) {
     const double g = S.gain[i]; const int rf = S.feat[i];
     int rank = 0;
     for (int j = 0; j < nl; ++j) {
@@ -585,7 +621,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
     S.rank[i] = rank;
   }
   if (tid == 0) s_count = 0;
-  __syncthreads();
+  SubSync(0);
   // expansions that are not committed yet (the batch's first leaf is certain to be committed by the next replay, the others
   // are speculative): bounding them bounds the nodes / pool slots a tree can consume to (L - 1) + spec_budget expansions
   const int outstanding = (ctrl->num_nodes - 1) / 2 - (nl - 1);
@@ -594,7 +630,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   int kmax = min(min(max_batch, 1 + spec_left), node_room);
   if (kmax < 1) kmax = 1;
   const int num_nodes = ctrl->num_nodes;
-  for (int i = tid; i < nl; i += blockDim.x) {
+  for (int i = tid; i < nl; i += kFindThreads) {
     const bool eligible = !S.exp[i] && S.gain[i] > 0.0 && S.rank[i] < budget;
     if (!eligible) continue;
     int pos = 0;
@@ -615,7 +651,7 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
       ctrl->batch[pos] = it;
     }
   }
-  __syncthreads();
+  SubSync(0);
   if (tid == 0) {
     const int bn = s_count;
     ctrl->batch_n = bn;
@@ -627,6 +663,16 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
     for (int k = 0; k < kMaxBatch; ++k) ctrl->part_cursor[k] = 0ULL;
     ctrl->part_ctas_done = 0;
   }
+}
+
+__global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, int* __restrict__ avail, BatchCtrl* __restrict__ ctrl,
+                                                   TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
+                                                   int max_nodes, int spec_budget, int max_batch) {
+  PdlLaunchDependents();
+  PdlWait();
+  if (ctrl->done) return;
+  extern __shared__ double sel_smem_raw[];
+  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw);
 }
 
 // ------------------------------------------------------------------------------------------------ K8 + K3 fused

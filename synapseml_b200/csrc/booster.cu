@@ -7,6 +7,7 @@
 
 #include "batch_tree.cuh"
 #include "kernels.cuh"
+#include "tree_persist.cuh"
 
 namespace lgb {
 
@@ -134,6 +135,18 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.leaf_parent = ip + 6 * L; tree_dev_.leaf_depth = ip + 7 * L;
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+  }
+  // single-GPU learner: one cooperative launch per tree (tree_persist.cuh) when the select scratch fits beside the histograms
+  persist_smem_ = kHistSmem + SelectSmemBytes(cfg_.num_leaves);
+  // Measured (C2, B200): 1.46 / 1.51 ms per iteration against 1.28 / 1.27 for the multi-kernel path at 30 / 500 iterations — the
+  // rounds are bound by chains of dependent L2 round trips inside the phases, not by launches — so it is opt-in
+  // (LGB_B200_PERSISTENT=1); it is kept as the base for an in-kernel peer-memory exchange.
+  use_persistent_ = false;
+  if (const char* env = getenv("LGB_B200_PERSISTENT"))
+    use_persistent_ = atoi(env) != 0 && !net_->active() && persist_smem_ <= size_t(227) * 1024;
+  if (use_persistent_) {
+    SetSmem(k_bt_tree<4, 4, false>, persist_smem_); SetSmem(k_bt_tree<2, 4, false>, persist_smem_); SetSmem(k_bt_tree<1, 4, false>, persist_smem_);
+    SetSmem(k_bt_tree<4, 2, true>, persist_smem_); SetSmem(k_bt_tree<2, 2, true>, persist_smem_); SetSmem(k_bt_tree<1, 2, true>, persist_smem_);
   }
   SetSmem(k_bt_select, SelectSmemBytes(1024));   // the largest tree the learner accepts; launches ask for what their num_leaves needs
 #define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
@@ -375,6 +388,44 @@ void Booster::LaunchFind(bool root) {
   ++launches_;
 }
 
+void Booster::LaunchTreeKernel() {
+  const BinLayout& lay = ds_->layout;
+  const int R = lay.rows_per_step;
+  const bool flt = !lp_.quantized;
+  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
+  TreeKernelArgs a;
+  a.rm = ds_->d_rm.p; a.rm_stride = static_cast<unsigned>(lay.rm_stride);
+  a.cm = ds_->d_cm.p; a.n_pad = static_cast<long long>(ds_->n_pad);
+  a.fmeta = ds_->d_fmeta.p;
+  a.gh16 = d_gh16_.p; a.ghfix = d_ghfix_.p;
+  a.idx0 = d_idx_[0].p; a.idx1 = d_idx_[1].p;
+  a.work = d_hist_work_.p; a.pool = d_hist_pool_.p;
+  a.nodes = d_nodes_; a.avail = d_avail_.p; a.ctrl = d_ctrl_;
+  a.feat_best = d_feat_best_.p; a.splittable = d_splittable_.p;
+  a.T = tree_dev_;
+  a.P = lp_;
+  a.F = F_; a.work_elems = work_elems_;
+  a.tiles = CeilDiv(F_, ft);
+  a.row_ctas = std::max(1, kNumSms / a.tiles);
+  if (flt) {
+    a.rows_per_flush = kFixRowsPerCopy * R;
+  } else {
+    const int qb = cfg_.num_grad_quant_bins;
+    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
+    a.rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
+  }
+  a.max_nodes = max_nodes_; a.spec_budget = spec_budget_; a.max_batch = max_batch_;
+  LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, sizeof(long long) * work_elems_, stream_));
+  const dim3 grid(kNumSms);      // one CTA per SM; tiles * row_ctas <= 148 of them build histograms, all take part in the other phases
+  void* args[] = {&a};
+  const void* fn;
+  if (!flt) fn = R == 4 ? (const void*)k_bt_tree<4, 4, false> : R == 2 ? (const void*)k_bt_tree<2, 4, false> : (const void*)k_bt_tree<1, 4, false>;
+  else fn = R == 4 ? (const void*)k_bt_tree<4, 2, true> : R == 2 ? (const void*)k_bt_tree<2, 2, true> : (const void*)k_bt_tree<1, 2, true>;
+  LGB_CUDA(cudaLaunchCooperativeKernel(fn, grid, dim3(kHistThreads), args, persist_smem_, stream_));
+  ++launches_;
+  ++hist_kernel_launches_;
+}
+
 // One round = expand every leaf of the current batch (partition, histogram of the smaller child, split search for both
 // children), then replay the sequential order and choose the next batch.  Every kernel reads its work from device memory
 // and returns at once when the tree is finished, so rounds are enqueued without waiting for the GPU.
@@ -405,6 +456,11 @@ void Booster::TrainTree(HostTree* out) {
   k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
+  if (use_persistent_ && !time_hist_ && !prof_) {
+    LaunchTreeKernel();
+    LGB_CHECK(FetchTree(out), "the persistent tree kernel returned before the tree was finished");
+    return;
+  }
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
   ProfBegin("select");

@@ -143,6 +143,8 @@ class Booster {
   double last_hist_ms_ = 0;
   int launches_ = 0;
   int work_elems_ = 0;
+  bool use_persistent_ = false;
+  size_t persist_smem_ = 0;
   int part_blocks_ = 592;                   // 4 x 148 SMs (k_bt_partition is built for 4 CTAs per SM)
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
@@ -164,6 +166,7 @@ class Booster {
   void LaunchHist(bool root);
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
+  void LaunchTreeKernel();
   bool FetchTree(HostTree* out);
   void UpdateScores();
   ModelHeader MakeHeader() const;

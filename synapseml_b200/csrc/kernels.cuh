@@ -306,9 +306,9 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
 }
 
 // Split search runs on 256-thread sub-blocks (one per feature x child); a CTA may hold more than one of them (the persistent
-// tree kernel runs two), so they synchronise on named barriers instead of __syncthreads().
+// tree kernel runs four), so they synchronise on named barriers instead of __syncthreads().
 constexpr int kFindThreads = 256;
-constexpr int kMaxFindSubs = 2;
+constexpr int kMaxFindSubs = 4;
 __device__ __forceinline__ void SubSync(int sub) { asm volatile("bar.sync %0, %1;" ::"r"(sub + 1), "n"(kFindThreads) : "memory"); }
 
 struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right: reverse, left: forward)

@@ -178,3 +178,24 @@ def test_full_size_properties(native):
     assert np.allclose(m.predict_raw(X[sub]), nb.scores()[sub], rtol=0, atol=1e-12)   # score update == tree traversal
     nb.free()
     nd.free()
+
+
+@pytest.mark.parametrize("mode", ["quantized", "float"])
+def test_opt_in_persistent_tree_kernel_gives_the_same_model(native, monkeypatch, mode):
+    """LGB_B200_PERSISTENT=1 grows each tree in one cooperative launch (tree_persist.cuh) from the same phase bodies."""
+    X, y = S.higgs_shape(60000)
+    params = "objective=binary num_leaves=31 max_bin=255 min_data_in_leaf=20 verbosity=-1"
+    if mode == "quantized":
+        params += " use_quantized_grad=true stochastic_rounding=false"
+    models = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("LGB_B200_PERSISTENT", flag)
+        nd = NativeDataset(X, y, params, micro_batches=[8192])
+        nb = NativeBooster(nd, params)
+        for _ in range(6):
+            nb.update()
+        models.append(strip_parameters(nb.model_string()))
+        nb.free()
+        nd.free()
+    assert models[0] == models[1]
+
