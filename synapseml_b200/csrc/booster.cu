@@ -301,7 +301,7 @@ void Booster::ComputeGradients() {
     a.truncation_level = cfg_.lambdarank_truncation_level; a.norm = cfg_.lambdarank_norm; a.table_size = 1024 * 1024;
     a.max_cnt = max_query_len_;
     const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
-    const size_t smem = static_cast<size_t>(max_query_len_) * (sizeof(double) + sizeof(float) + sizeof(int));
+    const size_t smem = static_cast<size_t>(max_query_len_) * (3 * sizeof(double) + 3 * sizeof(float) + sizeof(int) + 1) + 16;
     static size_t smem_set = 0;
     if (smem > smem_set) { SetSmem(k_grad_lambdarank, smem); smem_set = smem; }
     k_grad_lambdarank<<<nq, 256, smem, stream_>>>(a);

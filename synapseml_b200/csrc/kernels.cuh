@@ -71,9 +71,8 @@ __global__ void k_grad_l2(const double* __restrict__ score, const float* __restr
 }
 
 // LambdaRank-NDCG.  One CTA per query.  Step 1: stable rank of every document by score (descending) by counting, which
-// equals std::stable_sort's order.  Step 2: one thread per document replays exactly the pairs that touch it, in the
-// CPU's (i, j) order, so its float32 lambda/hessian sums are bit-identical to the sequential loop.  Step 3: thread 0
-// re-walks the pairs in (i, j) order for the double-precision sum_lambdas (needed for the log2 normalisation).
+// equals std::stable_sort's order.  Step 2 (k_grad_lambdarank): the pair loop, with every floating-point sum taken in the
+// sequential loop's order so float32 lambdas / hessians and the double sum behind the log2 normalisation are bit-identical.
 struct LambdarankArgs {
   const double* score; const float* label; const float* weight; const int* qb;
   const double* inv_max_dcg; const double* label_gain; const double* discount; const double* sigmoid_table;
@@ -111,15 +110,25 @@ __device__ __forceinline__ bool LrPair(const LambdarankArgs& a, const double* s_
   return true;
 }
 
-__global__ void k_grad_lambdarank(LambdarankArgs a) {
+// Every pair (i, j), i < min(cnt - 1, truncation), j > i, is evaluated ONCE, by the thread that owns document j in the
+// iteration of the (sequential) outer loop over i; the three order-sensitive accumulations of the CPU loop are kept in its
+// order: document j's float sums take their (i, j) terms in increasing i (own registers-in-shared), document i's float sums
+// take the (i, j) terms in increasing j (one thread walks the row that was just staged in shared memory), and the double
+// sum of lambdas for the normalisation walks the same row on another thread.
+__global__ void __launch_bounds__(256) k_grad_lambdarank(LambdarankArgs a) {
   extern __shared__ __align__(16) unsigned char lr_smem[];
   const int q = blockIdx.x;
   const int start = a.qb[q];
   const int cnt = a.qb[q + 1] - start;
   double* s_score = reinterpret_cast<double*>(lr_smem);                 // [max_cnt] sorted by rank
-  float* s_label = reinterpret_cast<float*>(s_score + a.max_cnt);      // [max_cnt]
-  int* s_doc = reinterpret_cast<int*>(s_label + a.max_cnt);            // rank -> doc
-  __shared__ double s_norm;
+  double* s_pl = s_score + a.max_cnt;                                   // staged row of pair lambdas
+  double* s_ph = s_pl + a.max_cnt;
+  float* s_label = reinterpret_cast<float*>(s_ph + a.max_cnt);         // [max_cnt]
+  float* s_lam = s_label + a.max_cnt;
+  float* s_hes = s_lam + a.max_cnt;
+  int* s_doc = reinterpret_cast<int*>(s_hes + a.max_cnt);              // rank -> doc
+  unsigned char* s_flag = reinterpret_cast<unsigned char*>(s_doc + a.max_cnt);   // bit 0: pair counted, bit 1: i is the higher label
+  __shared__ double s_sum;
   const double* sc = a.score + start;
   const float* lb = a.label + start;
   for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
@@ -130,7 +139,9 @@ __global__ void k_grad_lambdarank(LambdarankArgs a) {
       rank += (se > sd) || (se == sd && e < d);
     }
     s_score[rank] = sd; s_label[rank] = lb[d]; s_doc[rank] = d;
+    s_lam[rank] = 0.0f; s_hes[rank] = 0.0f;
   }
+  if (threadIdx.x == 0) s_sum = 0.0;
   __syncthreads();
   const double inverse_max_dcg = a.inv_max_dcg[q];
   const double best_score = s_score[0];
@@ -140,60 +151,59 @@ __global__ void k_grad_lambdarank(LambdarankArgs a) {
   const bool norm_on = a.norm && best_score != worst_score;
   const int T = a.truncation_level;
   const int imax = min(cnt - 1, T);      // i ranges over [0, imax)
-  for (int r = threadIdx.x; r < cnt; r += blockDim.x) {
-    float lam = 0.0f, hes = 0.0f;
-    if (s_score[r] != KMINSCORE) {
-      // as the later element j = r of pairs (i, r), i < min(r, imax)
-      for (int i = 0; i < min(r, imax); ++i) {
-        if (s_score[i] == KMINSCORE) continue;
+  for (int i = 0; i < imax; ++i) {
+    if (s_score[i] == KMINSCORE) continue;
+    for (int j = i + 1 + threadIdx.x; j < cnt; j += blockDim.x) {
+      unsigned char flag = 0;
+      if (s_score[j] != KMINSCORE) {
         double pl, ph; bool i_high;
-        if (!LrPair(a, s_score, s_label, i, r, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
-        if (i_high) lam -= static_cast<float>(pl); else lam += static_cast<float>(pl);   // r is low when i is high
-        hes += static_cast<float>(ph);
-      }
-      // as the earlier element i = r of pairs (r, j), j > r
-      if (r < imax) {
-        for (int j = r + 1; j < cnt; ++j) {
-          if (s_score[j] == KMINSCORE) continue;
-          double pl, ph; bool i_high;
-          if (!LrPair(a, s_score, s_label, r, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
-          if (i_high) lam += static_cast<float>(pl); else lam -= static_cast<float>(pl);
-          hes += static_cast<float>(ph);
+        if (LrPair(a, s_score, s_label, i, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) {
+          flag = 1 | (i_high ? 2 : 0);
+          s_pl[j] = pl; s_ph[j] = ph;
+          // document j is the lower one when i is the higher one
+          s_lam[j] = i_high ? s_lam[j] - static_cast<float>(pl) : s_lam[j] + static_cast<float>(pl);
+          s_hes[j] += static_cast<float>(ph);
         }
       }
+      s_flag[j] = flag;
     }
-    a.grad[start + s_doc[r]] = lam;
-    a.hess[start + s_doc[r]] = hes;
+    __syncthreads();
+    if (threadIdx.x == (i & 31)) {               // warp 0: document i's sums over its row, in increasing j
+      float lam = s_lam[i], hes = s_hes[i];
+      for (int j = i + 1; j < cnt; ++j) {
+        const unsigned char fl = s_flag[j];
+        if (!(fl & 1)) continue;
+        const float pl = static_cast<float>(s_pl[j]);
+        if (fl & 2) lam += pl; else lam -= pl;
+        hes += static_cast<float>(s_ph[j]);
+      }
+      s_lam[i] = lam; s_hes[i] = hes;
+    } else if (a.norm && threadIdx.x == 32 + (i & 31)) {   // warp 1: the double sum for the normalisation, same order
+      double sum = s_sum;
+      for (int j = i + 1; j < cnt; ++j)
+        if (s_flag[j] & 1) sum -= 2 * s_pl[j];
+      s_sum = sum;
+    }
+    __syncthreads();
   }
+  double nf = -1.0;
   if (a.norm) {
-    if (threadIdx.x == 0) {
-      double sum_lambdas = 0.0;
-      for (int i = 0; i < imax; ++i) {
-        if (s_score[i] == KMINSCORE) continue;
-        for (int j = i + 1; j < cnt; ++j) {
-          if (s_score[j] == KMINSCORE) continue;
-          double pl, ph; bool i_high;
-          if (!LrPair(a, s_score, s_label, i, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) continue;
-          sum_lambdas -= 2 * pl;
-        }
-      }
-      s_norm = (sum_lambdas > 0) ? SoftLog2(1 + sum_lambdas) / sum_lambdas : -1.0;
-    }
-    __syncthreads();
-    if (s_norm >= 0.0) {
-      const double nf = s_norm;
-      for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
-        a.grad[start + d] = static_cast<float>(a.grad[start + d] * nf);
-        a.hess[start + d] = static_cast<float>(a.hess[start + d] * nf);
-      }
-    }
+    const double sum_lambdas = s_sum;
+    nf = (sum_lambdas > 0) ? SoftLog2(1 + sum_lambdas) / sum_lambdas : -1.0;
   }
-  if (a.weight != nullptr) {
-    __syncthreads();
-    for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
-      a.grad[start + d] = static_cast<float>(a.grad[start + d] * a.weight[start + d]);
-      a.hess[start + d] = static_cast<float>(a.hess[start + d] * a.weight[start + d]);
+  for (int r = threadIdx.x; r < cnt; r += blockDim.x) {
+    float lam = s_lam[r], hes = s_hes[r];
+    if (nf >= 0.0) {
+      lam = static_cast<float>(lam * nf);
+      hes = static_cast<float>(hes * nf);
     }
+    const int d = start + s_doc[r];
+    if (a.weight != nullptr) {
+      lam = static_cast<float>(lam * a.weight[d]);
+      hes = static_cast<float>(hes * a.weight[d]);
+    }
+    a.grad[d] = lam;
+    a.hess[d] = hes;
   }
 }
 

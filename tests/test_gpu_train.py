@@ -194,7 +194,7 @@ def test_opt_in_persistent_tree_kernel_gives_the_same_model(native, monkeypatch,
         nb = NativeBooster(nd, params)
         for _ in range(6):
             nb.update()
-        models.append(strip_parameters(nb.model_string()))
+        models.append(strip_parameters(nb.model()))
         nb.free()
         nd.free()
     assert models[0] == models[1]
