@@ -33,16 +33,26 @@ struct NodeDev {
   int state;               // 0: leaf whose children are not known; 1: expanded (children known, split not committed); 2: committed
   int left, right;         // child nodes once expanded
   int pad_;
+  // what the replay needs to know about the children of an expanded node, written by the children's split search
+  // ([0] = left child, [1] = right child), so that it never has to chase the child nodes
+  int child_feat[2], child_count[2];
+  double child_gain[2];
   SplitDev best;
 };
 
+// Everything the kernels of a round need to know about one expansion.  Written by the select step; the outcome of the
+// partition (how many rows went left) is read from the item's cursor, so no kernel has to wait for a "publish" step:
+// ChildGeom() derives the children's row ranges, which child is the smaller one and whether they are searched at all.
 struct BatchItem {
-  int node, left, right;
+  int node, left, right;                        // parent node and the node ids reserved for its children
   int feature, threshold, default_left, nan_bin;
-  int src_begin, src_count, src_buf;
-  int smaller, larger, find;
-  int parent_slot;
-  int pad_[2];
+  int src_begin, src_count, src_buf;            // the parent's rows
+  int parent_slot, fresh_slot;                  // pool slots: the larger child takes over the parent's, the smaller gets the fresh one
+  int child_depth;
+  int search;                                   // 0: max_depth reached, the children are never searched
+  int est_left, est_right;                      // the split's count estimates (the data-parallel learner's global counts)
+  long long left_int_g, left_int_h, right_int_g, right_int_h;
+  double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
 };
 
 struct BatchCtrl {
@@ -53,17 +63,44 @@ struct BatchCtrl {
   int batch_n;
   int spec_used;           // expansions beyond the first of each batch so far (statistics)
   int rounds;
-  int pad_;
-  long long batch_rows;    // rows of all smaller children of the current batch (histogram CTAs are shared out by it)
+  int applied;             // the finished tree has been added to the scores
+  unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
   BatchItem batch[kMaxBatch];
   int find_count[kMaxBatch][2];
-  unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
-  int part_ctas_done;                          // CTAs of the running partition kernel that are finished
-  int applied;                                 // the finished tree has been added to the scores
   unsigned int max_abs_g_bits, max_abs_h_bits;
   double grad_scale, hess_scale, inv_grad_scale, inv_hess_scale;
   long long hist_rows, hist_launches;
+  // optional timeline for experiments (LGB_B200_TRACE=1): (event id, %globaltimer ns) pairs written by CTA 0 of every kernel
+  long long* trace;
+  int trace_n, trace_cap;
 };
+
+__device__ __forceinline__ void Trace(BatchCtrl* ctrl, int id) {
+  if (ctrl->trace == nullptr) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  const int i = atomicAdd(&ctrl->trace_n, 1);
+  if (i < ctrl->trace_cap) { ctrl->trace[2 * i] = id; ctrl->trace[2 * i + 1] = static_cast<long long>(t); }
+}
+#define LGB_TRACE(ctrl, id) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) Trace(ctrl, id); } while (0)
+
+struct ChildGeom {
+  int nl, nr;              // rows that went left / right on this GPU
+  int lc, rc;              // counts the split search uses: nl / nr (serial learner) or the estimates (data-parallel)
+  int buf;                 // index buffer the children live in
+  bool left_smaller, find;
+};
+__device__ __forceinline__ ChildGeom MakeGeom(const BatchItem& it, unsigned long long cursor, const LearnerParams& P) {
+  ChildGeom g;
+  g.nl = static_cast<int>(cursor >> 32);
+  g.nr = it.src_count - g.nl;
+  g.lc = P.dp ? it.est_left : g.nl;
+  g.rc = P.dp ? it.est_right : g.nr;
+  g.buf = it.src_buf < 0 ? 0 : 1 - it.src_buf;
+  g.left_smaller = g.lc < g.rc;
+  g.find = it.search != 0 && !(g.rc < P.min_data_in_leaf * 2 && g.lc < P.min_data_in_leaf * 2);      // BeforeFindBestSplit
+  return g;
+}
 
 // ------------------------------------------------------------------------------------------------ init
 __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArraysDev T, int L, int n_local, int n_global) {
@@ -80,13 +117,13 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
     NodeDev z;
     z.begin = 0; z.count = n_local; z.buf = -1; z.global_count = n_global; z.int_g = z.int_h = 0; z.sum_g = z.sum_h = 0.0;
     z.depth = 0; z.hist_slot = 0; z.state = 0; z.left = z.right = -1; z.pad_ = 0;
+    z.child_feat[0] = z.child_feat[1] = -1; z.child_count[0] = z.child_count[1] = 0; z.child_gain[0] = z.child_gain[1] = KMINSCORE;
     z.best = EmptySplit(-1, -1);
     nodes[0] = z;
     avail[0] = 0;
     ctrl->num_leaves = 1; ctrl->done = 0; ctrl->num_nodes = 1; ctrl->num_slots = 1; ctrl->batch_n = 0; ctrl->spec_used = 0;
-    ctrl->rounds = 0; ctrl->batch_rows = 0; ctrl->applied = 0;
+    ctrl->rounds = 0; ctrl->applied = 0;
     for (int k = 0; k < kMaxBatch; ++k) { ctrl->find_count[k][0] = 0; ctrl->find_count[k][1] = 0; ctrl->part_cursor[k] = 0ULL; }
-    ctrl->part_ctas_done = 0;
   }
 }
 
@@ -97,13 +134,14 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
 // mostly idle CTAs; that was 15 us of fixed cost per round.)
 // The body: all kHistThreads threads of a CTA; (cta_x, tile) = the CTA's place in a (row_ctas x tiles) arrangement.  The shared
 // histograms must be zero on entry and are zero again on return.
-struct HistShared { int node[kMaxBatch]; int chunks[kMaxBatch + 1]; int rpc; };
+struct HistShared { int begin[kMaxBatch], count[kMaxBatch], buf[kMaxBatch]; int chunks[kMaxBatch + 1]; int rpc; };
 
 template <int R, int BPL, bool FLT, bool ROOT>
 __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16,
                                          const int2* __restrict__ ghfix, const int* idx0, const int* idx1, const NodeDev* nodes,
                                          BatchCtrl* ctrl, long long* work, int work_elems, int F, int rows_per_flush, int row_ctas,
-                                         int cta_x, int tile, unsigned int* hsm, unsigned lane_addr, HistShared* sh) {
+                                         int cta_x, int tile, unsigned int* hsm, unsigned lane_addr, HistShared* sh,
+                                         const LearnerParams& P) {
   constexpr int LPR = 32 / R;
   constexpr int FT = LPR * BPL;
   const int lane = threadIdx.x & 31;
@@ -116,11 +154,21 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
     long long total = 0;
     int active = 0;
     for (int k = 0; k < kMaxBatch; ++k) {
-      int nd = -1;
-      if (ROOT) { if (k == 0) nd = 0; }
-      else if (k < bn && ctrl->batch[k].find) nd = ctrl->batch[k].smaller;
-      sh->node[k] = nd;
-      if (nd >= 0) { total += nodes[nd].count; ++active; }
+      int cnt = 0;
+      if (ROOT) {
+        if (k == 0) { sh->begin[0] = 0; sh->buf[0] = -1; cnt = nodes[0].count; active = 1; }
+      } else if (k < bn) {
+        const BatchItem& it = ctrl->batch[k];
+        const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
+        if (g.find) {
+          sh->begin[k] = g.left_smaller ? it.src_begin : it.src_begin + g.nl;
+          sh->buf[k] = g.buf;
+          cnt = g.left_smaller ? g.nl : g.nr;
+          ++active;
+        }
+      }
+      sh->count[k] = cnt;       // an item with an empty smaller child (possible on one GPU of several) needs no CTA
+      total += cnt;
     }
     const int avail_ctas = max(1, row_ctas - active);
     long long rpc = (total + avail_ctas - 1) / avail_ctas;
@@ -130,13 +178,11 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
     int c = 0;
     for (int k = 0; k < kMaxBatch; ++k) {
       sh->chunks[k] = c;
-      if (sh->node[k] >= 0) {
-        const int cnt = nodes[sh->node[k]].count;
-        c += (cnt + rows_per_cta - 1) / rows_per_cta;
-        if (cta_x == 0 && tile == 0) {
-          atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(cnt));
-          atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
-        }
+      const int cnt = sh->count[k];
+      c += (cnt + rows_per_cta - 1) / rows_per_cta;
+      if (cnt > 0 && cta_x == 0 && tile == 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), static_cast<unsigned long long>(cnt));
+        atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), 1ULL);
       }
     }
     sh->chunks[kMaxBatch] = c;
@@ -147,8 +193,7 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
   for (int chunk = cta_x; chunk < total_chunks; chunk += row_ctas) {      // normally one chunk per CTA
     int k = 0;
     while (k + 1 < kMaxBatch && chunk >= sh->chunks[k + 1]) ++k;
-    const NodeDev& nd = nodes[sh->node[k]];
-    const int begin = nd.begin, count = nd.count, buf = nd.buf;
+    const int begin = sh->begin[k], count = sh->count[k], buf = sh->buf[k];
     const int lo = (chunk - sh->chunks[k]) * rows_per_cta;
     const int hi = min(count, lo + rows_per_cta);
     const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
@@ -162,7 +207,8 @@ template <int R, int BPL, bool FLT, bool ROOT>
 __global__ void __launch_bounds__(kHistThreads, 1)
 k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
           const int* __restrict__ idx0, const int* __restrict__ idx1, const NodeDev* __restrict__ nodes,
-          BatchCtrl* __restrict__ ctrl, long long* __restrict__ work, int work_elems, int F, int rows_per_flush, int row_ctas) {
+          BatchCtrl* __restrict__ ctrl, long long* __restrict__ work, int work_elems, int F, int rows_per_flush, int row_ctas,
+          LearnerParams P) {
   extern __shared__ unsigned int hsm_raw[];
   __shared__ HistShared sh;
   PdlLaunchDependents();
@@ -171,11 +217,14 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
   const unsigned lane_addr = sbase + (threadIdx.x & 31) * 4;
   for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;      // before the wait: overlaps the predecessor
+  LGB_TRACE(ctrl, 20);
   PdlWait();
+  LGB_TRACE(ctrl, 21);
   if (ctrl->done) return;
   __syncthreads();
   HistBody<R, BPL, FLT, ROOT>(rm, rm_stride, gh16, ghfix, idx0, idx1, nodes, ctrl, work, work_elems, F, rows_per_flush, row_ctas,
-                              blockIdx.x, blockIdx.y, hsm, lane_addr, &sh);
+                              blockIdx.x, blockIdx.y, hsm, lane_addr, &sh, P);
+  LGB_TRACE(ctrl, 22);
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6
@@ -194,19 +243,47 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   double* s_gain = s_gain_all[sub]; int* s_feat = s_feat_all[sub]; int* s_idx = s_idx_all[sub];
   const int F = P.num_features;
   const int b = threadIdx.x & (kFindThreads - 1);
-  int node, parent = -1, parent_slot = 0;
-  if (root) node = 0;
-  else {
+  // ---- which node is this, and what do we know about it
+  NodeDev me;              // what gets published for the child (root: only the fields the search needs)
+  int node, parent = -1, parent_slot = 0, side = 0;
+  bool find = true;
+  if (root) {
+    node = 0;
+    me = nodes[0];
+  } else {
     const BatchItem& it = ctrl->batch[k];
-    node = c == 0 ? it.smaller : it.larger;
+    const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
+    const bool is_left = (c == 0) == g.left_smaller;      // c == 0: the smaller child (its histogram was just built)
+    node = is_left ? it.left : it.right;
+    side = is_left ? 0 : 1;
     parent = it.node;
     parent_slot = it.parent_slot;
+    find = g.find;
+    me.begin = is_left ? it.src_begin : it.src_begin + g.nl;
+    me.count = is_left ? g.nl : g.nr;
+    me.buf = g.buf;
+    me.global_count = is_left ? g.lc : g.rc;
+    me.int_g = is_left ? it.left_int_g : it.right_int_g; me.int_h = is_left ? it.left_int_h : it.right_int_h;
+    me.sum_g = is_left ? it.left_sum_g : it.right_sum_g; me.sum_h = is_left ? it.left_sum_h : it.right_sum_h;
+    me.depth = it.child_depth;
+    me.hist_slot = c == 0 ? it.fresh_slot : it.parent_slot;     // the larger child takes over the parent's slot
+    me.state = 0; me.left = me.right = -1; me.pad_ = 0;
+  }
+  me.child_feat[0] = me.child_feat[1] = -1; me.child_count[0] = me.child_count[1] = 0; me.child_gain[0] = me.child_gain[1] = KMINSCORE;
+  if (!find) {         // children that are not searched are published by their first unit alone
+    if (f != 0) return;
+    if (b == 0) {
+      me.best = EmptySplit(-1, -1);
+      nodes[node] = me;
+      nodes[parent].child_gain[side] = KMINSCORE; nodes[parent].child_feat[side] = -1; nodes[parent].child_count[side] = me.global_count;
+      __threadfence();
+    }
+    return;
   }
   const FeatureMetaDev fm = fmeta[f];
   const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
   const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
   const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
-  const NodeDev& Nd = nodes[node];
   longlong2 v;
   if (QUANT) {     // packed work area: (sum g << 32) + sum h
     const long long pk = work[static_cast<size_t>(root ? 0 : k) * work_elems + static_cast<size_t>(f) * kBins + b];
@@ -223,25 +300,21 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
       v.x = p.x - v.x; v.y = p.y - v.y;
     }
   }
-  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(Nd.hist_slot) * slot_stride + off) = v;
+  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
   SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
   unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
+  long long tg = me.int_g, th = me.int_h;
   if (!used) {
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
-    long long tg, th;
-    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, Nd.int_g, Nd.int_h, Nd.sum_g, Nd.sum_h, Nd.global_count, P, gscale, hscale,
+    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
                          fb + f, spl, &tg, &th, sub);
-    if (root && f == 0 && b == 0) {
-      nodes[0].int_g = tg; nodes[0].int_h = th;
-      nodes[0].sum_g = static_cast<double>(tg) * gscale; nodes[0].sum_h = static_cast<double>(th) * hscale;
-    }
   }
   __threadfence();
   SubSync(sub);
   if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == F - 1);
   SubSync(sub);
-  if (s_last) {       // the last unit of this child reduces over the features
+  if (s_last) {       // the last unit of this child reduces over the features and publishes the child
     __threadfence();
     double bg = KMINSCORE; int bf = -1, bi = -1;
     for (int j = b; j < F; j += kFindThreads) {
@@ -261,7 +334,16 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
       bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
       for (int w = 1; w < 8; ++w)
         if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
-      nodes[node].best = fb[bi];
+      if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
+        me.int_g = tg; me.int_h = th;
+        me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
+      }
+      me.best = fb[bi];
+      nodes[node] = me;
+      if (!root) {
+        nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
+        nodes[parent].child_count[side] = me.global_count;
+      }
       ctrl->find_count[root ? 0 : k][c] = 0;
     }
   }
@@ -274,11 +356,14 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
                                                  BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
                                                  unsigned char* __restrict__ splittable, LearnerParams P, int root) {
   PdlLaunchDependents();
+  LGB_TRACE(ctrl, 30);
   PdlWait();
+  LGB_TRACE(ctrl, 31);
   if (ctrl->done) return;
   const int k = blockIdx.z;
-  if (!root && (k >= ctrl->batch_n || !ctrl->batch[k].find)) return;
+  if (!root && k >= ctrl->batch_n) return;
   FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, blockIdx.x, blockIdx.y, k, 0);
+  LGB_TRACE(ctrl, 32);
 }
 
 // ------------------------------------------------------------------------------------------------ K7 (batched, one pass)
@@ -288,46 +373,10 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
 // high word, right count in the low word) and writes the entries to the other index buffer: lefts grow from the front of
 // the parent's range, rights from its back.  Inside a tile the order is kept; tiles land in the order their atomics arrive.
 // Every sum taken over a leaf's rows is an exact integer sum (quantized or fixed-point gradients), so the order of rows
-// inside a leaf does not change any result.  The last tile of a leaf publishes the two children.
+// inside a leaf does not change any result.  Nothing is "published" at the end: the consumers of the round (histogram, split
+// search) derive the children's row ranges from the final cursor value (MakeGeom).
 constexpr int kPartTileWords = 64;                        // 8 words per warp, 8 warps
 constexpr int kPartTileRows = kPartTileWords * 32;
-
-// Publishes the two children of batch item k once all its rows are placed (what DataPartition::Split and the leaf-splits
-// initialisation do in the reference learner).  One thread.
-__device__ __forceinline__ void PublishChildren(BatchCtrl* ctrl, NodeDev* nodes, int k, const LearnerParams& P) {
-  const BatchItem it = ctrl->batch[k];
-  const int n = it.src_count, begin = it.src_begin;
-  const int other = it.src_buf < 0 ? 0 : 1 - it.src_buf;
-  const unsigned long long cur = atomicAdd(&ctrl->part_cursor[k], 0ULL);
-  const int total = static_cast<int>(cur >> 32);
-  const NodeDev par = nodes[it.node];
-  const SplitDev bs = par.best;
-  const int nl_true = total, nr_true = n - total;
-  int lc = bs.left_count, rc = bs.right_count;
-  if (!P.dp) { lc = nl_true; rc = nr_true; }       // serial learner: true partition counts replace the estimates
-  NodeDev L, Rr;
-  const int depth = par.depth + 1;
-  L.begin = begin; L.count = nl_true; L.buf = other; L.global_count = lc;
-  L.int_g = bs.left_int_g; L.int_h = bs.left_int_h; L.sum_g = bs.left_sum_g; L.sum_h = bs.left_sum_h; L.depth = depth;
-  Rr.begin = begin + nl_true; Rr.count = nr_true; Rr.buf = other; Rr.global_count = rc;
-  Rr.int_g = bs.right_int_g; Rr.int_h = bs.right_int_h; Rr.sum_g = bs.right_sum_g; Rr.sum_h = bs.right_sum_h; Rr.depth = depth;
-  L.state = Rr.state = 0; L.left = L.right = Rr.left = Rr.right = -1; L.pad_ = Rr.pad_ = 0;
-  L.best = EmptySplit(-1, -1); Rr.best = EmptySplit(-1, -1);
-  const bool left_smaller = lc < rc;
-  const int fresh_slot = atomicAdd(&ctrl->num_slots, 1);
-  // the larger child takes over the parent's pool slot (parent - smaller is formed in place), the smaller gets a fresh one
-  L.hist_slot = left_smaller ? fresh_slot : par.hist_slot;
-  Rr.hist_slot = left_smaller ? par.hist_slot : fresh_slot;
-  bool find = true;                                  // BeforeFindBestSplit
-  if (P.max_depth > 0 && depth >= P.max_depth) find = false;
-  if (rc < P.min_data_in_leaf * 2 && lc < P.min_data_in_leaf * 2) find = false;
-  nodes[it.left] = L; nodes[it.right] = Rr;
-  nodes[it.node].state = 1; nodes[it.node].left = it.left; nodes[it.node].right = it.right;
-  ctrl->batch[k].smaller = left_smaller ? it.left : it.right;
-  ctrl->batch[k].larger = left_smaller ? it.right : it.left;
-  ctrl->batch[k].find = find ? 1 : 0;
-  if (find) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->batch_rows), static_cast<unsigned long long>(left_smaller ? nl_true : nr_true));
-}
 
 // Tile list of the round (one thread): tiles[k] = first tile of batch item k, tiles[kMaxBatch] = total.
 __device__ __forceinline__ void PartTileList(const BatchCtrl* ctrl, int bn, int* tiles) {
@@ -435,30 +484,22 @@ __global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t*
                                                                const int* __restrict__ idx0r, const int* __restrict__ idx1r,
                                                                int* __restrict__ idx0w, int* __restrict__ idx1w,
                                                                const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
-                                                               BatchCtrl* __restrict__ ctrl, NodeDev* __restrict__ nodes,
-                                                               long long* __restrict__ work, int work_elems, LearnerParams P) {
+                                                               BatchCtrl* __restrict__ ctrl, long long* __restrict__ work,
+                                                               int work_elems) {
   PdlLaunchDependents();
+  LGB_TRACE(ctrl, 10);
   PdlWait();
+  LGB_TRACE(ctrl, 11);
   if (ctrl->done) return;
   const int bn = ctrl->batch_n;
   __shared__ int s_tiles[kMaxBatch + 1];
-  __shared__ int s_lastcta;
   // the histograms of this batch accumulate into work[0..bn) with atomics: clear them here
   for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < static_cast<size_t>(bn) * work_elems; i += static_cast<size_t>(gridDim.x) * blockDim.x)
     work[i] = 0;
   if (threadIdx.x == 0) PartTileList(ctrl, bn, s_tiles);
   __syncthreads();
   PartitionTiles<ES>(cm, n_pad, idx0r, idx1r, idx0w, idx1w, gh16, ghfix, ctrl, bn, s_tiles, blockIdx.x, gridDim.x, 0);
-  // the CTA that finishes last publishes the children of the whole batch
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_lastcta = (atomicAdd(&ctrl->part_ctas_done, 1) == static_cast<int>(gridDim.x) - 1);
-  __syncthreads();
-  if (s_lastcta) {
-    __threadfence();
-    if (threadIdx.x < bn) PublishChildren(ctrl, nodes, threadIdx.x, P);
-    if (threadIdx.x == 0) ctrl->part_ctas_done = 0;
-  }
+  LGB_TRACE(ctrl, 12);
 }
 
 // ------------------------------------------------------------------------------------------------ replay + next batch
@@ -470,17 +511,25 @@ __global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t*
 //   P3  thread 0 applies the order-dependent bookkeeping of Tree::Split (parent/child links, depths, leaf values) in commit order;
 //   P4  per-leaf arrays are written back and the next batch is chosen.
 struct SelectSmem {
-  double *gain, *cgain0, *cgain1, *lvalue, *lweight, *c_lo, *c_ro, *c_lw, *c_rw;
-  int *feat, *node, *rank, *cfeat0, *cfeat1, *cnode0, *cnode1, *lparent, *ldepth, *lcount, *c_leaf, *c_node, *c_lc, *c_rc;
+  double *gain, *cgain0, *cgain1, *lvalue, *lweight, *p_lo, *p_ro, *p_lw, *p_rw;
+  int *feat, *node, *rank, *cfeat0, *cfeat1, *cnode0, *cnode1, *lparent, *ldepth, *lcount, *c_leaf, *c_node, *p_lc, *p_rc, *p_feature,
+      *p_threshold, *p_flags;
+  float* p_gain;
   unsigned char *exp, *isleft;
 };
-constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 14 * sizeof(int) + 2;
+constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 17 * sizeof(int) + sizeof(float) + 2;
 __host__ __device__ inline size_t SelectSmemBytes(int L) { return kSelectSmemPerLeaf * static_cast<size_t>((L + 7) & ~7) + 64; }
 
-// The body: 256 threads (threadIdx.x < 256 of one CTA), synchronised with the named barrier of sub-block 0.
+// The body: one 256-thread sub-block, synchronised with its named barrier.
+//   P0  every thread loads one available leaf: its candidate split and, if it is expanded, what a commit needs (the split, the
+//       children's candidates and counts — all in the leaf's own node record) plus the per-leaf tree arrays;
+//   P1  warp 0 replays the sequential leaf choice and records the commit list;
+//   P2  thread j writes the order-independent tree fields of commit j (from shared memory);
+//   P3  thread 0 applies the order-dependent bookkeeping of Tree::Split (parent/child links, depths, leaf values) in commit order;
+//   P4  per-leaf arrays are written back and the next batch is chosen.
 __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl* ctrl, const TreeArraysDev& T,
                                            const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P, int max_nodes,
-                                           int spec_budget, int max_batch, double* sel_smem_raw) {
+                                           int spec_budget, int max_batch, double* sel_smem_raw, int sub) {
   __shared__ int s_state, s_nl, s_m, s_count;
   const int L = P.num_leaves;
   const int Lc = (L + 7) & ~7;
@@ -488,15 +537,17 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   {
     double* d = sel_smem_raw;
     S.gain = d; d += Lc; S.cgain0 = d; d += Lc; S.cgain1 = d; d += Lc; S.lvalue = d; d += Lc; S.lweight = d; d += Lc;
-    S.c_lo = d; d += Lc; S.c_ro = d; d += Lc; S.c_lw = d; d += Lc; S.c_rw = d; d += Lc;
+    S.p_lo = d; d += Lc; S.p_ro = d; d += Lc; S.p_lw = d; d += Lc; S.p_rw = d; d += Lc;
     int* q = reinterpret_cast<int*>(d);
     S.feat = q; q += Lc; S.node = q; q += Lc; S.rank = q; q += Lc; S.cfeat0 = q; q += Lc; S.cfeat1 = q; q += Lc;
     S.cnode0 = q; q += Lc; S.cnode1 = q; q += Lc; S.lparent = q; q += Lc; S.ldepth = q; q += Lc; S.lcount = q; q += Lc;
-    S.c_leaf = q; q += Lc; S.c_node = q; q += Lc; S.c_lc = q; q += Lc; S.c_rc = q; q += Lc;
+    S.c_leaf = q; q += Lc; S.c_node = q; q += Lc; S.p_lc = q; q += Lc; S.p_rc = q; q += Lc; S.p_feature = q; q += Lc;
+    S.p_threshold = q; q += Lc; S.p_flags = q; q += Lc;
+    S.p_gain = reinterpret_cast<float*>(q); q += Lc;
     unsigned char* c = reinterpret_cast<unsigned char*>(q);
     S.exp = c; c += Lc; S.isleft = c;
   }
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x & (kFindThreads - 1), lane = tid & 31;
   const int nl0 = ctrl->num_leaves;
   // ---- P0
   for (int i = tid; i < nl0; i += kFindThreads) {
@@ -506,17 +557,23 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     const bool e = N.state == 1;
     S.exp[i] = e;
     if (e) {
-      const int l = N.left, r = N.right;
-      S.cnode0[i] = l; S.cnode1[i] = r;
-      S.cgain0[i] = nodes[l].best.gain; S.cfeat0[i] = nodes[l].best.real_feature;
-      S.cgain1[i] = nodes[r].best.gain; S.cfeat1[i] = nodes[r].best.real_feature;
+      S.cnode0[i] = N.left; S.cnode1[i] = N.right;
+      S.cgain0[i] = N.child_gain[0]; S.cfeat0[i] = N.child_feat[0];
+      S.cgain1[i] = N.child_gain[1]; S.cfeat1[i] = N.child_feat[1];
+      const double lo = N.best.left_output, ro = N.best.right_output;
+      S.p_lo[i] = (lo != lo) ? 0.0 : lo; S.p_ro[i] = (ro != ro) ? 0.0 : ro;
+      S.p_lw[i] = N.best.left_sum_h; S.p_rw[i] = N.best.right_sum_h;
+      S.p_lc[i] = N.child_count[0]; S.p_rc[i] = N.child_count[1];
+      S.p_feature[i] = N.best.feature; S.p_threshold[i] = N.best.threshold;
+      S.p_flags[i] = (N.best.default_left ? 2 : 0) | ((N.best.missing_type & 3) << 2);      // = Tree's decision_type
+      S.p_gain[i] = static_cast<float>(N.best.gain);
     }
     const int par = T.leaf_parent[i];
     S.lparent[i] = par; S.ldepth[i] = T.leaf_depth[i]; S.lvalue[i] = T.leaf_value[i]; S.lweight[i] = T.leaf_weight[i];
     S.lcount[i] = T.leaf_count[i];
     S.isleft[i] = par >= 0 ? (T.left_child[par] == ~i) : 0;
   }
-  SubSync(0);
+  SubSync(sub);
   // ---- P1: replay the sequential order as far as the already expanded leaves allow (warp 0)
   if (tid < 32) {
     int nl = nl0, m = 0, state = 0;
@@ -549,36 +606,24 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     }
     if (lane == 0) { s_state = state; s_nl = nl; s_m = m; }
   }
-  SubSync(0);
+  SubSync(sub);
   const int nl = s_nl, m = s_m;
-  // ---- P2: order-independent fields of every commit
+  // ---- P2: order-independent fields of every commit (a leaf id commits at most once per replay, so the commit data loaded
+  //      for it in P0 is still the committed node's)
   for (int j = tid; j < m; j += kFindThreads) {
-    const int nd = S.c_node[j], best_leaf = S.c_leaf[j];
+    const int best_leaf = S.c_leaf[j];
     const int new_node = nl0 - 1 + j, new_leaf = nl0 + j;
-    const NodeDev& par = nodes[nd];
-    const int lnode = par.left, rnode = par.right;
-    const int feature = par.best.feature, threshold = par.best.threshold, default_left = par.best.default_left;
-    const double gain = par.best.gain, lo = par.best.left_output, ro = par.best.right_output;
-    const double lw = par.best.left_sum_h, rw = par.best.right_sum_h;
-    const int lc = nodes[lnode].global_count, rc = nodes[rnode].global_count;
-    const int missing_type = fmeta[feature].missing_type;
-    T.split_feature_inner[new_node] = feature;
-    T.split_gain[new_node] = static_cast<float>(gain);
+    T.split_feature_inner[new_node] = S.p_feature[best_leaf];
+    T.split_gain[new_node] = S.p_gain[best_leaf];
     T.left_child[new_node] = ~best_leaf;
     T.right_child[new_node] = ~new_leaf;
-    T.internal_weight[new_node] = lw + rw;
-    T.internal_count[new_node] = lc + rc;
-    signed char dt = 0;
-    if (default_left) dt |= 2;
-    dt |= static_cast<signed char>((missing_type & 3) << 2);
-    T.decision_type[new_node] = dt;
-    T.threshold_in_bin[new_node] = threshold;
-    nodes[nd].state = 2;
-    S.c_lo[j] = (lo != lo) ? 0.0 : lo; S.c_ro[j] = (ro != ro) ? 0.0 : ro;
-    S.c_lw[j] = lw; S.c_rw[j] = rw; S.c_lc[j] = lc; S.c_rc[j] = rc;
+    T.internal_weight[new_node] = S.p_lw[best_leaf] + S.p_rw[best_leaf];
+    T.internal_count[new_node] = S.p_lc[best_leaf] + S.p_rc[best_leaf];
+    T.decision_type[new_node] = static_cast<signed char>(S.p_flags[best_leaf]);
+    T.threshold_in_bin[new_node] = S.p_threshold[best_leaf];
+    nodes[S.c_node[j]].state = 2;
   }
-  SubSync(0);
-  // ---- P3: order-dependent bookkeeping
+  // ---- P3: order-dependent bookkeeping (reads only what P0 / P1 left in shared memory)
   if (tid == 0) {
     for (int j = 0; j < m; ++j) {
       const int best_leaf = S.c_leaf[j], new_node = nl0 - 1 + j, new_leaf = nl0 + j;
@@ -589,13 +634,13 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       T.internal_value[new_node] = S.lvalue[best_leaf];
       S.lparent[best_leaf] = new_node; S.lparent[new_leaf] = new_node;
       S.isleft[best_leaf] = 1; S.isleft[new_leaf] = 0;
-      S.lvalue[best_leaf] = S.c_lo[j]; S.lweight[best_leaf] = S.c_lw[j]; S.lcount[best_leaf] = S.c_lc[j];
-      S.lvalue[new_leaf] = S.c_ro[j]; S.lweight[new_leaf] = S.c_rw[j]; S.lcount[new_leaf] = S.c_rc[j];
+      S.lvalue[new_leaf] = S.p_ro[best_leaf]; S.lweight[new_leaf] = S.p_rw[best_leaf]; S.lcount[new_leaf] = S.p_rc[best_leaf];
+      S.lvalue[best_leaf] = S.p_lo[best_leaf]; S.lweight[best_leaf] = S.p_lw[best_leaf]; S.lcount[best_leaf] = S.p_lc[best_leaf];
       S.ldepth[new_leaf] = S.ldepth[best_leaf] + 1;
       S.ldepth[best_leaf] += 1;
     }
   }
-  SubSync(0);
+  SubSync(sub);
   // ---- P4: write the per-leaf arrays back
   if (m > 0) {
     for (int i = tid; i < nl; i += kFindThreads) {
@@ -621,15 +666,15 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     S.rank[i] = rank;
   }
   if (tid == 0) s_count = 0;
-  SubSync(0);
+  SubSync(sub);
   // expansions that are not committed yet (the batch's first leaf is certain to be committed by the next replay, the others
   // are speculative): bounding them bounds the nodes / pool slots a tree can consume to (L - 1) + spec_budget expansions
-  const int outstanding = (ctrl->num_nodes - 1) / 2 - (nl - 1);
+  const int num_nodes = ctrl->num_nodes, num_slots = ctrl->num_slots;
+  const int outstanding = (num_nodes - 1) / 2 - (nl - 1);
   const int spec_left = max(0, spec_budget - outstanding);
-  const int node_room = (max_nodes - ctrl->num_nodes) / 2;
+  const int node_room = (max_nodes - num_nodes) / 2;
   int kmax = min(min(max_batch, 1 + spec_left), node_room);
   if (kmax < 1) kmax = 1;
-  const int num_nodes = ctrl->num_nodes;
   for (int i = tid; i < nl; i += kFindThreads) {
     const bool eligible = !S.exp[i] && S.gain[i] > 0.0 && S.rank[i] < budget;
     if (!eligible) continue;
@@ -640,28 +685,33 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       atomicAdd(&s_count, 1);
       const int nd = S.node[i];
       const NodeDev& par = nodes[nd];
-      const int feature = par.best.feature;
-      const FeatureMetaDev fm = fmeta[feature];
+      const SplitDev& bs = par.best;
       BatchItem it;
       it.node = nd; it.left = num_nodes + 2 * pos; it.right = it.left + 1;
-      it.feature = feature; it.threshold = par.best.threshold; it.default_left = par.best.default_left;
-      it.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
+      it.feature = bs.feature; it.threshold = bs.threshold; it.default_left = bs.default_left;
+      it.nan_bin = bs.nan_bin;
       it.src_begin = par.begin; it.src_count = par.count; it.src_buf = par.buf;
-      it.smaller = it.larger = -1; it.find = 0; it.parent_slot = par.hist_slot; it.pad_[0] = it.pad_[1] = 0;
+      it.parent_slot = par.hist_slot; it.fresh_slot = num_slots + pos;
+      it.child_depth = par.depth + 1;
+      it.search = !(P.max_depth > 0 && it.child_depth >= P.max_depth);
+      it.est_left = bs.left_count; it.est_right = bs.right_count;
+      it.left_int_g = bs.left_int_g; it.left_int_h = bs.left_int_h; it.right_int_g = bs.right_int_g; it.right_int_h = bs.right_int_h;
+      it.left_sum_g = bs.left_sum_g; it.left_sum_h = bs.left_sum_h; it.right_sum_g = bs.right_sum_g; it.right_sum_h = bs.right_sum_h;
+      nodes[nd].state = 1; nodes[nd].left = it.left; nodes[nd].right = it.right;      // expanded by the time the next replay runs
       ctrl->batch[pos] = it;
     }
   }
-  SubSync(0);
+  SubSync(sub);
   if (tid == 0) {
     const int bn = s_count;
     ctrl->batch_n = bn;
     ctrl->num_nodes = num_nodes + 2 * bn;
+    ctrl->num_slots = num_slots + bn;
     ctrl->spec_used += bn - 1;      // statistics only
     ctrl->num_leaves = nl;
-    ctrl->batch_rows = 0;
     ctrl->rounds += 1;
+   
     for (int k = 0; k < kMaxBatch; ++k) ctrl->part_cursor[k] = 0ULL;
-    ctrl->part_ctas_done = 0;
   }
 }
 
@@ -669,10 +719,13 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
                                                    TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
                                                    int max_nodes, int spec_budget, int max_batch) {
   PdlLaunchDependents();
+  LGB_TRACE(ctrl, 40);
   PdlWait();
+  LGB_TRACE(ctrl, 41);
   if (ctrl->done) return;
   extern __shared__ double sel_smem_raw[];
-  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw);
+  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw, 0);
+  LGB_TRACE(ctrl, 42);
 }
 
 // ------------------------------------------------------------------------------------------------ K8 + K3 fused

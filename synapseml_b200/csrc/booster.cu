@@ -117,6 +117,15 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   LGB_CUDA(cudaMalloc(&d_nodes_, sizeof(NodeDev) * max_nodes_));
   LGB_CUDA(cudaMalloc(&d_ctrl_, sizeof(BatchCtrl)));
   LGB_CUDA(cudaMemset(d_ctrl_, 0, sizeof(BatchCtrl)));
+  if (getenv("LGB_B200_TRACE") != nullptr) {      // experiments only: per-kernel timeline of the tree kernels
+    trace_cap_ = 1 << 16;
+    d_trace_.AllocZero(static_cast<size_t>(2) * trace_cap_);
+    BatchCtrl hc;
+    memset(&hc, 0, sizeof(hc));
+    hc.trace = nullptr; hc.trace_cap = trace_cap_;
+    LGB_CUDA(cudaMemcpy(d_ctrl_, &hc, sizeof(hc), cudaMemcpyHostToDevice));
+    if (const char* from = getenv("LGB_B200_TRACE_FROM")) trace_from_ = atoi(from);
+  }
   d_avail_.AllocZero(L);
   d_feat_best_.Alloc(static_cast<size_t>(2) * kMaxBatch * std::max(F_, 1));
   d_splittable_.Alloc(static_cast<size_t>(max_nodes_) * std::max(F_, 1));
@@ -160,6 +169,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
 Booster::~Booster() {
   cudaSetDevice(device_);
   try { ProfReport(); } catch (...) {}
+  try { DumpTrace(); } catch (...) {}
   if (d_nodes_) cudaFree(d_nodes_);
   if (d_ctrl_) cudaFree(d_ctrl_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
@@ -189,6 +199,20 @@ void Booster::ProfReport() {
   }
   prof_recs_.clear();
   for (auto& kv : agg) fprintf(stderr, "[prof] %-16s n=%6d total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second, 1e3 * kv.second.second / kv.second.first);
+}
+
+void Booster::DumpTrace() {
+  if (trace_cap_ == 0) return;
+  BatchCtrl hc;
+  LGB_CUDA(cudaMemcpy(&hc, d_ctrl_, sizeof(hc), cudaMemcpyDeviceToHost));
+  const int n = std::min(hc.trace_n, trace_cap_);
+  std::vector<long long> t(static_cast<size_t>(2) * n);
+  LGB_CUDA(cudaMemcpy(t.data(), d_trace_.p, sizeof(long long) * 2 * n, cudaMemcpyDeviceToHost));
+  const char* path = getenv("LGB_B200_TRACE");
+  FILE* f = fopen(path, "w");
+  if (!f) return;
+  for (int i = 0; i < n; ++i) fprintf(f, "%lld %lld\n", t[2 * i], t[2 * i + 1]);
+  fclose(f);
 }
 
 void Booster::Sync() const { LGB_CUDA(cudaStreamSynchronize(stream_)); }
@@ -356,7 +380,7 @@ void Booster::LaunchHist(bool root) {
     LGB_CUDA(cudaEventRecord(e0, stream_));
   }
 #define LAUNCH_HIST_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, d_idx_[0].p, d_idx_[1].p, \
-                         d_nodes_, d_ctrl_, d_hist_work_.p, work_elems_, F_, rows_per_flush, row_ctas
+                         d_nodes_, d_ctrl_, d_hist_work_.p, work_elems_, F_, rows_per_flush, row_ctas, lp_
 #define LAUNCH_HIST(RR, BPL, FLT)                                                                                     \
   do {                                                                                                                \
     if (root) LaunchPdl(k_bt_hist<RR, BPL, FLT, true>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);  \
@@ -385,6 +409,16 @@ void Booster::LaunchFind(bool root) {
   else
     LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, d_hist_work_.p, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
               d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0);
+  ++launches_;
+}
+
+// Replay + next batch.  (Running it inside the split-search kernel's last sub-block was measured: no faster — the replay's own
+// ~10 us stay on the critical path and the search kernel loses registers.)
+void Booster::LaunchSelect() {
+  ProfBegin("select");
+  LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p,
+            lp_, max_nodes_, spec_budget_, max_batch_);
+  ProfEnd();
   ++launches_;
 }
 
@@ -434,18 +468,15 @@ void Booster::EnqueueRounds(int rounds) {
     ProfBegin("partition");
     if (idx_es_ == 2)
       LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_hist_work_.p, work_elems_, lp_);
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_hist_work_.p, work_elems_);
     else
       LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_nodes_, d_hist_work_.p, work_elems_, lp_);
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_hist_work_.p, work_elems_);
     ProfEnd();
     ProfBegin("hist"); LaunchHist(false); ProfEnd();
     ProfBegin("find"); LaunchFind(false); ProfEnd();
-    ProfBegin("select");
-    LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
-              spec_budget_, max_batch_);
-    ProfEnd();
-    launches_ += 2;
+    LaunchSelect();
+    launches_ += 1;
   }
 }
 
@@ -453,6 +484,11 @@ void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
   hist_events_used_ = 0;
+  if (trace_cap_ > 0) {      // trace three trees starting at iteration LGB_B200_TRACE_FROM
+    long long* p = (iter_ >= trace_from_ && iter_ < trace_from_ + 3) ? d_trace_.p : nullptr;
+    LGB_CUDA(cudaMemcpyAsync(&d_ctrl_->trace, &p, sizeof(p), cudaMemcpyHostToDevice, stream_));
+    LGB_CUDA(cudaStreamSynchronize(stream_));
+  }
   k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n, static_cast<int>(n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
@@ -463,11 +499,7 @@ void Booster::TrainTree(HostTree* out) {
   }
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
-  ProfBegin("select");
-  LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p, lp_, max_nodes_,
-            spec_budget_, max_batch_);
-  ProfEnd();
-  ++launches_;
+  LaunchSelect();
   // the number of rounds a tree needs is only known on the device: enqueue as many as the previous tree used (+1), then look
   int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + 1) : std::min(L - 1, (L - 1) / 2 + 2);
   int total = 0;

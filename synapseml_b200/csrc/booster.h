@@ -28,6 +28,7 @@ struct SplitDev {
   double left_output, right_output;
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
   long long left_int_g, left_int_h, right_int_g, right_int_h;
+  int missing_type, nan_bin;   // of the split feature (nan_bin = -1: none), so that later stages need no feature table lookup
 };
 
 struct LeafDev {
@@ -143,6 +144,8 @@ class Booster {
   double last_hist_ms_ = 0;
   int launches_ = 0;
   int work_elems_ = 0;
+  DevBuf<long long> d_trace_;
+  int trace_cap_ = 0, trace_from_ = 0;
   bool use_persistent_ = false;
   size_t persist_smem_ = 0;
   int part_blocks_ = 592;                   // 4 x 148 SMs (k_bt_partition is built for 4 CTAs per SM)
@@ -167,6 +170,8 @@ class Booster {
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
   void LaunchTreeKernel();
+  void LaunchSelect();
+  void DumpTrace();
   bool FetchTree(HostTree* out);
   void UpdateScores();
   ModelHeader MakeHeader() const;

@@ -312,6 +312,7 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
   s.left_count = s.right_count = 0; s.left_output = s.right_output = 0.0;
   s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
   s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
+  s.missing_type = 0; s.nan_bin = -1;
   return s;
 }
 
@@ -470,6 +471,8 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   if (b == 0) {
     const bool any = s_flag != 0;
     SplitDev s = EmptySplit(f, fm.real_index);
+    s.missing_type = fm.missing_type;
+    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;

@@ -7,7 +7,7 @@
 // phases of a round are separated by cooperative-groups grid syncs (~1.3 us each, experiments/grid_sync_probe.py) instead of
 // kernel boundaries:
 //     root :  histogram | split search | select
-//     round:  partition (+ clear work areas; last CTA publishes the children) | histogram of the smaller children |
+//     round:  partition (+ clear work areas) | histogram of the smaller children |
 //             split search of both children (sibling by subtraction; last unit of a child reduces over features) | select
 // The phase bodies are the device functions the stand-alone kernels use (PartitionTiles, HistBody, FindUnit, SelectBody), so
 // both paths produce the same trees.  Everything that changes during the kernel (index buffers, work areas, pool, nodes,
@@ -43,7 +43,7 @@ constexpr int kTreeSubs = kHistThreads / kFindThreads;      // 256-thread sub-bl
 
 template <bool QUANT>
 __device__ __forceinline__ void TreeFindPhase(const TreeKernelArgs& a, bool root, int* s_units /*[kMaxBatch + 1]*/) {
-  // units = (batch slot with find, child, feature); every sub-block of the grid takes units round-robin
+  // units = (batch slot, child, feature); every sub-block of the grid takes units round-robin
   BatchCtrl* ctrl = a.ctrl;
   const int F = a.F;
   const int sub = threadIdx.x >> 8;
@@ -52,7 +52,7 @@ __device__ __forceinline__ void TreeFindPhase(const TreeKernelArgs& a, bool root
     const int bn = root ? 1 : ctrl->batch_n;
     for (int k = 0; k < kMaxBatch; ++k) {
       s_units[k] = u;
-      if (k < bn && (root || ctrl->batch[k].find)) u += (root ? 1 : 2) * F;
+      if (k < bn) u += (root ? 1 : 2) * F;
     }
     s_units[kMaxBatch] = u;
   }
@@ -74,7 +74,6 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_bt_tree(const TreeKernelArg
   extern __shared__ unsigned int hsm_raw[];
   __shared__ HistShared s_hist;
   __shared__ int s_list[kMaxBatch + 1];
-  __shared__ int s_lastcta;
   constexpr int ES = FLT ? 4 : 2;
   cg::grid_group grid = cg::this_grid();
   BatchCtrl* ctrl = a.ctrl;
@@ -91,12 +90,12 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_bt_tree(const TreeKernelArg
   // ---- root
   if (hist_cta)
     HistBody<R, BPL, FLT, true>(a.rm, a.rm_stride, a.gh16, a.ghfix, a.idx0, a.idx1, a.nodes, ctrl, a.work, a.work_elems, a.F,
-                                a.rows_per_flush, a.row_ctas, cta_x, tile, hsm, lane_addr, &s_hist);
+                                a.rows_per_flush, a.row_ctas, cta_x, tile, hsm, lane_addr, &s_hist, a.P);
   grid.sync();
   TreeFindPhase<!FLT>(a, true, s_list);
   grid.sync();
   if (blockIdx.x == 0 && threadIdx.x < kFindThreads)
-    SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem);
+    SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0);
   grid.sync();
   // ---- rounds
   while (!ctrl->done) {
@@ -108,24 +107,15 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_bt_tree(const TreeKernelArg
     __syncthreads();
     PartitionTiles<ES>(a.cm, a.n_pad, a.idx0, a.idx1, a.idx0, a.idx1, a.gh16, a.ghfix, ctrl, bn, s_list, blockIdx.x * kTreeSubs + sub,
                        gridDim.x * kTreeSubs, sub);
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) s_lastcta = (atomicAdd(&ctrl->part_ctas_done, 1) == static_cast<int>(gridDim.x) - 1);
-    __syncthreads();
-    if (s_lastcta) {
-      __threadfence();
-      if (threadIdx.x < bn) PublishChildren(ctrl, a.nodes, threadIdx.x, a.P);
-      if (threadIdx.x == 0) ctrl->part_ctas_done = 0;
-    }
     grid.sync();
     if (hist_cta)
       HistBody<R, BPL, FLT, false>(a.rm, a.rm_stride, a.gh16, a.ghfix, a.idx0, a.idx1, a.nodes, ctrl, a.work, a.work_elems, a.F,
-                                   a.rows_per_flush, a.row_ctas, cta_x, tile, hsm, lane_addr, &s_hist);
+                                   a.rows_per_flush, a.row_ctas, cta_x, tile, hsm, lane_addr, &s_hist, a.P);
     grid.sync();
     TreeFindPhase<!FLT>(a, false, s_list);
     grid.sync();
     if (blockIdx.x == 0 && threadIdx.x < kFindThreads)
-      SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem);
+      SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0);
     grid.sync();
   }
 }
