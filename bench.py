@@ -125,6 +125,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--rows", type=int, default=N_ROWS)
+    # strong (default): the named 10M-row dataset is sharded over the GPUs; weak: every GPU gets --rows rows (information only)
+    ap.add_argument("--scaling", choices=["strong", "weak"], default="strong")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -152,7 +154,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group(backend="cpu:gloo,cuda:nccl", rank=rank, world_size=world)
-    N = args.rows
+    N = args.rows * (world if args.scaling == "weak" else 1)
     lo, hi = N * rank // world, N * (rank + 1) // world
     X, y = S.higgs_shape(hi - lo, start=lo)
 
@@ -275,7 +277,7 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         cb, _ = cpu_baseline(steps=5, warmup=1)
     out = {"metric": "lightgbm_train_rows_iters_per_sec", "value": value, "unit": "rows*iters/s", "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
+           "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": args.scaling,
            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
            "config": {"workload": WORKLOAD, "rows": N, "features": N_FEAT, "rows_per_gpu": n_local, "parallelism": "dp%d" % world,
                       "l2": "inputs larger than L2 (binned matrix %d MB per GPU + 2x%d MB index buffers vs 126 MB L2)" % (n_local * 32 >> 20, n_local * 4 >> 20),

@@ -10,6 +10,7 @@ last_end = None
 agg = collections.defaultdict(list)
 for id_, t in ev:
     k, ph = id_ // 10, id_ % 10
+    if k not in names: continue
     if ph == 0: cur[k] = [t, None, None]
     elif ph == 1 and k in cur: cur[k][1] = t
     elif ph == 2 and k in cur and cur[k][1] is not None:
