@@ -145,6 +145,24 @@ int LGBM_B200_BoosterTimerStart(BoosterHandle handle);
 int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms);
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
 
+/* ---- scoring.  Prediction runs on the GPU of the calling process (one thread per row walks the trees);
+ * a booster loaded from a model string can only predict and save.
+ * LoadModelFromString: LGBM/booster/LightGBMBooster.scala:41-49 (the model string is shipped to the executors and a booster is
+ *   rebuilt there).  Supported: what this library writes (num_class = 1, numerical splits, no linear trees).
+ * PredictForMat / PredictForMatSingleRow: the C functions behind the SWIG overload LGBM_BoosterPredictForMatSingle
+ *   (LGBM/booster/LightGBMBooster.scala:520-557, called per row from the scoring UDF with thread-local output buffers).
+ *   predict_type 0 = normal (sigmoid for binary), 1 = raw score, 2 = leaf index; 3 (feature contributions) returns -1.
+ *   The single-row form costs one kernel launch and one device round trip per call: batch rows through PredictForMat. */
+int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out);
+int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
+                               int64_t* out_len);
+int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                              int predict_type, int start_iteration, int num_iteration, const char* parameter, int64_t* out_len,
+                              double* out_result);
+int LGBM_BoosterPredictForMatSingleRow(BoosterHandle handle, const void* data, int data_type, int ncol, int is_row_major,
+                                       int predict_type, int start_iteration, int num_iteration, const char* parameter,
+                                       int64_t* out_len, double* out_result);
+
 /* No counterpart in the reference.  Histogram (kernel K4, root-leaf case) for callers that may not allocate device memory:
  * an executor plugin living inside an external memory pool or a fixed per-task GPU budget, or a loop that must not take the
  * driver's allocation lock.  Its scratch (int64 accumulation area + descriptors, about 1 MB) is a static array in the

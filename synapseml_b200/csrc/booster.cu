@@ -7,6 +7,7 @@
 
 #include "batch_tree.cuh"
 #include "kernels.cuh"
+#include "predict_kernel.cuh"
 #include "tree_persist.cuh"
 
 namespace lgb {
@@ -167,6 +168,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
 }
 
 Booster::~Booster() {
+  if (device_ < 0) return;      // a loaded model that never predicted owns nothing on a GPU
   cudaSetDevice(device_);
   try { ProfReport(); } catch (...) {}
   try { DumpTrace(); } catch (...) {}
@@ -584,6 +586,7 @@ void Booster::UpdateScores() {
 
 // ---------------------------------------------------------------------------------------------------- GBDT
 bool Booster::UpdateOneIter() {
+  LGB_CHECK(!predict_only_, "this booster was loaded from a model string and can only predict");
   LGB_CUDA(cudaSetDevice(device_));
   const double kEps = 1e-15f;
   double init_score = 0.0;
@@ -652,9 +655,11 @@ bool Booster::UpdateOneIter() {
     }
   }
   models_.push_back(std::move(tree));
+  ++model_version_;
   if (!should_continue) {
     LogWarning("Stopped training because there are no more leaves that meet the split requirements");
     if (models_.size() > 1) models_.pop_back();
+    ++model_version_;
     Sync();
     return true;
   }
@@ -667,6 +672,7 @@ bool Booster::UpdateOneIterCustom(const float*, const float*) {
 }
 
 ModelHeader Booster::MakeHeader() const {
+  if (predict_only_) return loaded_header_;
   ModelHeader h;
   h.max_feature_idx = ds_->num_total_features - 1;
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
@@ -710,12 +716,105 @@ void Booster::CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const {
   scales[0] = hc.grad_scale; scales[1] = hc.hess_scale;
 }
 
-void Booster::PredictRaw(const double* data, int nrow, int ncol, double* out) const {
-  LGB_CHECK(ncol == ds_->num_total_features, "PredictRaw: expected %d columns, got %d", ds_->num_total_features, ncol);
-  for (int i = 0; i < nrow; ++i) {
-    double v = 0.0;
-    for (const auto& t : models_) v += t.Predict(data + static_cast<size_t>(i) * ncol);
-    out[i] = v;
+// ---------------------------------------------------------------------------------------------------- scoring
+Booster::Booster(const std::string& model_str) : ds_(nullptr) {
+  predict_only_ = true;
+  ParseModelString(model_str, &loaded_header_, &models_);
+  const std::string& o = loaded_header_.objective;
+  if (o.rfind("binary", 0) == 0) {
+    obj_ = kBinary;
+    const size_t p = o.find("sigmoid:");
+    if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
+  } else if (o.rfind("lambdarank", 0) == 0) {
+    obj_ = kLambdarank;
+  } else {
+    LGB_CHECK(o.rfind("regression", 0) == 0, "Model string: objective '%s' is not supported by this library", o.c_str());
+    obj_ = kL2;
+  }
+  for (auto& kv : loaded_header_.parameters) cfg_.raw[kv.first] = kv.second;
+  device_ = -1;      // resolved at the first prediction: loading and re-saving a model needs no GPU
+  iter_ = static_cast<int>(models_.size());
+  model_version_ = 1;
+}
+
+int Booster::NumTotalFeatures() const { return predict_only_ ? loaded_header_.max_feature_idx + 1 : ds_->num_total_features; }
+
+void Booster::TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const {
+  const int n = static_cast<int>(models_.size());
+  *t0 = std::min(std::max(0, start_iteration), n);
+  *t1 = num_iteration > 0 ? std::min(n, *t0 + num_iteration) : n;
+}
+
+int64_t Booster::CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const {
+  int t0, t1;
+  TreeRange(start_iteration, num_iteration, &t0, &t1);
+  return predict_type == kPredictLeaf ? nrow * (t1 - t0) : nrow;
+}
+
+void Booster::UploadModel() {
+  if (uploaded_version_ == model_version_) return;
+  std::vector<int> node_off(1, 0), leaf_off(1, 0), feat, left, right;
+  std::vector<double> thr, leaf;
+  std::vector<signed char> dt;
+  for (const HostTree& t : models_) {
+    const int ni = t.num_leaves - 1;
+    for (int i = 0; i < ni; ++i) {
+      feat.push_back(t.split_feature[i]); thr.push_back(t.threshold[i]); dt.push_back(t.decision_type[i]);
+      left.push_back(t.left_child[i]); right.push_back(t.right_child[i]);
+    }
+    for (int i = 0; i < t.num_leaves; ++i) leaf.push_back(t.leaf_value[i]);
+    node_off.push_back(static_cast<int>(feat.size()));
+    leaf_off.push_back(static_cast<int>(leaf.size()));
+  }
+  auto up = [&](auto& buf, const auto& v) {
+    buf.Alloc(std::max<size_t>(v.size(), 1));
+    if (!v.empty()) LGB_CUDA(cudaMemcpyAsync(buf.p, v.data(), sizeof(v[0]) * v.size(), cudaMemcpyHostToDevice, stream_));
+  };
+  up(dp_node_off_, node_off); up(dp_leaf_off_, leaf_off); up(dp_feat_, feat); up(dp_left_, left); up(dp_right_, right);
+  up(dp_thr_, thr); up(dp_leaf_, leaf); up(dp_dt_, dt);
+  LGB_CUDA(cudaStreamSynchronize(stream_));      // the host vectors go out of scope
+  uploaded_version_ = model_version_;
+}
+
+void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int ncol, bool row_major, int predict_type,
+                            int start_iteration, int num_iteration, double* out, int64_t* out_len) {
+  LGB_CHECK(data_type == 0 || data_type == 1, "Predict: data_type must be C_API_DTYPE_FLOAT32 or FLOAT64");
+  LGB_CHECK(predict_type == kPredictNormal || predict_type == kPredictRaw || predict_type == kPredictLeaf,
+            "Predict: predict_type %d (feature contributions) is not supported by this library yet", predict_type);
+  LGB_CHECK(ncol == NumTotalFeatures(), "Predict: expected %d columns, got %d", NumTotalFeatures(), ncol);
+  LGB_CHECK(nrow >= 0, "Predict: negative row count");
+  if (device_ < 0) device_ = ResolveDevice(cfg_);
+  LGB_CUDA(cudaSetDevice(device_));
+  UploadModel();
+  int t0, t1;
+  TreeRange(start_iteration, num_iteration, &t0, &t1);
+  const int per_row = predict_type == kPredictLeaf ? (t1 - t0) : 1;
+  if (out_len) *out_len = nrow * per_row;
+  if (nrow == 0 || per_row == 0) return;
+  PredModelDev m;
+  m.node_off = dp_node_off_.p; m.leaf_off = dp_leaf_off_.p; m.split_feature = dp_feat_.p; m.threshold = dp_thr_.p;
+  m.decision_type = dp_dt_.p; m.left = dp_left_.p; m.right = dp_right_.p; m.leaf_value = dp_leaf_.p;
+  const size_t esz = data_type == 1 ? sizeof(double) : sizeof(float);
+  // row-major input is processed in chunks of rows; column-major input in one piece
+  const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
+  dp_in_.Alloc(static_cast<size_t>(chunk_rows) * ncol * esz);
+  dp_out_.Alloc(static_cast<size_t>(chunk_rows) * per_row);
+  const int sig_on = obj_ == kBinary ? 1 : 0;
+  for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
+    const int64_t nr = std::min(chunk_rows, nrow - r0);
+    const unsigned char* src = static_cast<const unsigned char*>(data) + (row_major ? static_cast<size_t>(r0) * ncol * esz : 0);
+    LGB_CUDA(cudaMemcpyAsync(dp_in_.p, src, static_cast<size_t>(nr) * ncol * esz, cudaMemcpyHostToDevice, stream_));
+    const long long rs = row_major ? ncol : 1, cs = row_major ? 1 : nr;
+    const int grid = static_cast<int>(std::min<int64_t>(CeilDiv(static_cast<int>(std::min<int64_t>(nr, 1 << 30)), 128), kNumSms * 16));
+    if (data_type == 1)
+      k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, predict_type, sig_on,
+                                                   cfg_.sigmoid, dp_out_.p);
+    else
+      k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, predict_type, sig_on,
+                                                  cfg_.sigmoid, dp_out_.p);
+    LGB_CUDA(cudaGetLastError());
+    LGB_CUDA(cudaMemcpyAsync(out + static_cast<size_t>(r0) * per_row, dp_out_.p, sizeof(double) * nr * per_row, cudaMemcpyDeviceToHost, stream_));
+    LGB_CUDA(cudaStreamSynchronize(stream_));
   }
 }
 

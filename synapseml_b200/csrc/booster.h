@@ -65,6 +65,8 @@ struct LearnerParams {
 class Booster {
  public:
   Booster(Dataset* train, const char* params);
+  // scoring-only booster rebuilt from a model string (LGBM_BoosterLoadModelFromString); touches the GPU at the first prediction
+  explicit Booster(const std::string& model_str);
   ~Booster();
   bool UpdateOneIter();
   bool UpdateOneIterCustom(const float* grad, const float* hess);
@@ -75,7 +77,13 @@ class Booster {
   void CopyScores(double* out) const;
   void CopyGradients(float* g, float* h) const;
   void CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const;
-  void PredictRaw(const double* data, int nrow, int ncol, double* out) const;
+  // GPU prediction on raw feature values (predict_kernel.cuh).  data_type: 0 float32, 1 float64; predict_type: 0 normal, 1 raw,
+  // 2 leaf index.  Trees [start_iteration, start_iteration + num_iteration) (num_iteration <= 0: to the end).
+  void PredictForMat(const void* data, int data_type, int64_t nrow, int ncol, bool row_major, int predict_type, int start_iteration,
+                     int num_iteration, double* out, int64_t* out_len);
+  int64_t CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const;
+  int NumTotalFeatures() const;
+  bool predict_only() const { return predict_only_; }
   const Dataset* train() const { return ds_; }
 
   // Kernel-level hooks used by parity tests, bench.py's roofline measurement and the profiler (no host sync inside):
@@ -109,6 +117,16 @@ class Booster {
   bool need_train_ = true, has_weights_ = false;
   double label_weights_[2] = {1.0, 1.0};
   std::vector<HostTree> models_;
+  // scoring: the model flattened into device arrays (re-uploaded when the model changed)
+  bool predict_only_ = false;
+  ModelHeader loaded_header_;
+  long long model_version_ = 0, uploaded_version_ = -1;
+  DevBuf<int> dp_node_off_, dp_leaf_off_, dp_feat_, dp_left_, dp_right_;
+  DevBuf<double> dp_thr_, dp_leaf_, dp_out_;
+  DevBuf<signed char> dp_dt_;
+  DevBuf<unsigned char> dp_in_;
+  void UploadModel();
+  void TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const;
 
   // device state
   DevBuf<double> d_score_;

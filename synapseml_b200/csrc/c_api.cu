@@ -246,7 +246,7 @@ int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int
 }
 
 int LGBM_BoosterGetNumClasses(BoosterHandle, int* out_len) { API_BEGIN(); *out_len = 1; API_END(); }
-int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->train()->num_total_features; API_END(); }
+int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->NumTotalFeatures(); API_END(); }
 int LGBM_BoosterNumModelPerIteration(BoosterHandle, int* out) { API_BEGIN(); *out = 1; API_END(); }
 int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->NumTrees(); API_END(); }
 int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->CurrentIteration(); API_END(); }
@@ -255,6 +255,7 @@ int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len,
   API_BEGIN();
   LGB_CHECK(data_idx == 0, "LGBM_BoosterGetPredict: only the training data (data_idx 0) is available");
   auto b = static_cast<Booster*>(handle);
+  LGB_CHECK(!b->predict_only(), "LGBM_BoosterGetPredict: a booster loaded from a model string has no training data");
   *out_len = b->train()->num_data;
   b->CopyScores(out_result);
   API_END();
@@ -348,7 +349,40 @@ int LGBM_B200_BoosterTimerStart(BoosterHandle handle) { API_BEGIN(); static_cast
 int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms) { API_BEGIN(); *out_ms = static_cast<Booster*>(handle)->TimerStop(); API_END(); }
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out) {
   API_BEGIN();
-  static_cast<Booster*>(handle)->PredictRaw(data, nrow, ncol, out);
+  int64_t n = 0;
+  static_cast<Booster*>(handle)->PredictForMat(data, 1, nrow, ncol, true, 1, 0, -1, out, &n);
+  API_END();
+}
+
+// ---- scoring
+int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out) {
+  API_BEGIN();
+  if (model_str == nullptr) throw std::runtime_error("LoadModelFromString: model string is null");
+  std::unique_ptr<Booster> b(new Booster(std::string(model_str)));
+  if (out_num_iterations) *out_num_iterations = b->CurrentIteration();
+  *out = b.release();
+  API_END();
+}
+int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
+                               int64_t* out_len) {
+  API_BEGIN();
+  *out_len = static_cast<Booster*>(handle)->CalcNumPredict(num_row, predict_type, start_iteration, num_iteration);
+  API_END();
+}
+int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                              int predict_type, int start_iteration, int num_iteration, const char* /*parameter*/, int64_t* out_len,
+                              double* out_result) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->PredictForMat(data, data_type, nrow, ncol, is_row_major != 0, predict_type, start_iteration,
+                                               num_iteration, out_result, out_len);
+  API_END();
+}
+int LGBM_BoosterPredictForMatSingleRow(BoosterHandle handle, const void* data, int data_type, int ncol, int is_row_major,
+                                       int predict_type, int start_iteration, int num_iteration, const char* /*parameter*/,
+                                       int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->PredictForMat(data, data_type, 1, ncol, is_row_major != 0, predict_type, start_iteration, num_iteration,
+                                               out_result, out_len);
   API_END();
 }
 

@@ -3,6 +3,10 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <sstream>
+#include <stdexcept>
 
 namespace lgb {
 
@@ -121,6 +125,113 @@ std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& tre
   for (auto& kv : h.parameters) s += "[" + kv.first + ": " + kv.second + "]\n";
   s += "end of parameters\n\npandas_categorical:null\n";
   return s;
+}
+
+namespace {
+std::vector<std::string> SplitWs(const std::string& v) {
+  std::vector<std::string> out;
+  std::istringstream is(v);
+  std::string t;
+  while (is >> t) out.push_back(t);
+  return out;
+}
+template <typename T, typename F>
+void ParseList(const std::map<std::string, std::string>& kv, const char* key, size_t n, std::vector<T>* out, F conv) {
+  auto it = kv.find(key);
+  if (it == kv.end()) throw std::runtime_error(std::string("Model string: tree block lacks '") + key + "'");
+  const std::vector<std::string> tok = SplitWs(it->second);
+  if (tok.size() != n) throw std::runtime_error(std::string("Model string: '") + key + "' has " + std::to_string(tok.size()) +
+                                                " values, expected " + std::to_string(n));
+  out->resize(n);
+  for (size_t i = 0; i < n; ++i) (*out)[i] = conv(tok[i]);
+}
+}  // namespace
+
+void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostTree>* trees) {
+  *h = ModelHeader();
+  trees->clear();
+  std::istringstream is(text);
+  std::string line;
+  auto kv_of = [](const std::string& l, std::string* k, std::string* v) {
+    const size_t eq = l.find('=');
+    if (eq == std::string::npos) return false;
+    *k = l.substr(0, eq); *v = l.substr(eq + 1);
+    return true;
+  };
+  // ---- header
+  bool saw_tree_word = false;
+  std::map<std::string, std::string> cur;
+  bool in_tree = false, in_params = false;
+  auto finish_tree = [&]() {
+    if (!in_tree) return;
+    HostTree t;
+    auto geti = [&](const char* k) { auto it = cur.find(k); if (it == cur.end()) throw std::runtime_error(std::string("Model string: tree block lacks '") + k + "'"); return atoi(it->second.c_str()); };
+    t.num_leaves = geti("num_leaves");
+    if (cur.count("num_cat") && atoi(cur["num_cat"].c_str()) != 0) throw std::runtime_error("Model string: categorical splits are not supported by this library");
+    if (cur.count("is_linear") && atoi(cur["is_linear"].c_str()) != 0) throw std::runtime_error("Model string: linear trees are not supported by this library");
+    if (t.num_leaves < 1) throw std::runtime_error("Model string: num_leaves < 1");
+    auto toi = [](const std::string& x) { return atoi(x.c_str()); };
+    auto tod = [](const std::string& x) { return strtod(x.c_str(), nullptr); };
+    auto tof = [](const std::string& x) { return strtof(x.c_str(), nullptr); };
+    auto to8 = [](const std::string& x) { return static_cast<int8_t>(atoi(x.c_str())); };
+    const size_t nl = static_cast<size_t>(t.num_leaves), ni = nl - 1;
+    if (t.num_leaves > 1) {
+      ParseList(cur, "split_feature", ni, &t.split_feature, toi);
+      ParseList(cur, "split_gain", ni, &t.split_gain, tof);
+      ParseList(cur, "threshold", ni, &t.threshold, tod);
+      ParseList(cur, "decision_type", ni, &t.decision_type, to8);
+      ParseList(cur, "left_child", ni, &t.left_child, toi);
+      ParseList(cur, "right_child", ni, &t.right_child, toi);
+      ParseList(cur, "leaf_value", nl, &t.leaf_value, tod);
+      if (cur.count("leaf_weight")) ParseList(cur, "leaf_weight", nl, &t.leaf_weight, tod); else t.leaf_weight.assign(nl, 0.0);
+      if (cur.count("leaf_count")) ParseList(cur, "leaf_count", nl, &t.leaf_count, toi); else t.leaf_count.assign(nl, 0);
+      if (cur.count("internal_value")) ParseList(cur, "internal_value", ni, &t.internal_value, tod); else t.internal_value.assign(ni, 0.0);
+      if (cur.count("internal_weight")) ParseList(cur, "internal_weight", ni, &t.internal_weight, tod); else t.internal_weight.assign(ni, 0.0);
+      if (cur.count("internal_count")) ParseList(cur, "internal_count", ni, &t.internal_count, toi); else t.internal_count.assign(ni, 0);
+      for (size_t i = 0; i < ni; ++i) {
+        const int l = t.left_child[i], r = t.right_child[i];
+        auto ok = [&](int c) { return c >= 0 ? c < static_cast<int>(ni) : ~c < t.num_leaves; };
+        if (!ok(l) || !ok(r) || t.split_feature[i] < 0 || t.split_feature[i] > h->max_feature_idx)
+          throw std::runtime_error("Model string: tree " + std::to_string(trees->size()) + " has an out-of-range child or feature index");
+      }
+      t.split_feature_inner = t.split_feature;      // a loaded model has no bin mappers: inner indices and bin thresholds are unknown
+      t.threshold_in_bin.assign(ni, 0);
+    } else {
+      ParseList(cur, "leaf_value", 1, &t.leaf_value, tod);
+    }
+    t.shrinkage = cur.count("shrinkage") ? strtod(cur["shrinkage"].c_str(), nullptr) : 1.0;
+    trees->push_back(std::move(t));
+    cur.clear();
+    in_tree = false;
+  };
+  while (std::getline(is, line)) {
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    if (line.empty()) continue;
+    if (in_params) {
+      if (line == "end of parameters") { in_params = false; continue; }
+      if (line.size() > 2 && line.front() == '[' && line.back() == ']') {
+        const size_t c = line.find(": ");
+        if (c != std::string::npos) h->parameters.emplace_back(line.substr(1, c - 1), line.substr(c + 2, line.size() - c - 3));
+      }
+      continue;
+    }
+    if (line == "tree") { saw_tree_word = true; continue; }
+    if (line == "end of trees") { finish_tree(); continue; }
+    if (line == "parameters:") { finish_tree(); in_params = true; continue; }
+    if (line == "feature_importances:" || line.rfind("pandas_categorical", 0) == 0) { finish_tree(); continue; }
+    std::string k, v;
+    if (!kv_of(line, &k, &v)) continue;
+    if (k == "Tree") { finish_tree(); in_tree = true; continue; }
+    if (in_tree) { cur[k] = v; continue; }
+    if (k == "max_feature_idx") h->max_feature_idx = atoi(v.c_str());
+    else if (k == "objective") h->objective = v;
+    else if (k == "feature_names") h->feature_names = SplitWs(v);
+    else if (k == "feature_infos") h->feature_infos = SplitWs(v);
+    else if (k == "num_class") { if (atoi(v.c_str()) != 1) throw std::runtime_error("Model string: num_class != 1 is not supported by this library"); }
+    else if (k == "num_tree_per_iteration") { if (atoi(v.c_str()) != 1) throw std::runtime_error("Model string: num_tree_per_iteration != 1 is not supported by this library"); }
+  }
+  finish_tree();
+  if (!saw_tree_word) throw std::runtime_error("Model string does not start with 'tree'");
 }
 
 std::string FormatG17(double v) { return G17(v); }

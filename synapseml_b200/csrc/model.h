@@ -36,4 +36,10 @@ struct ModelHeader {
 
 std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration);
 
+// Inverse of ModelToString for the subset this library writes (num_class = 1, no categorical splits, no linear trees):
+// what LGBM_BoosterLoadModelFromString reads when the Scala side rebuilds a booster from the model string on an executor
+// (lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:41-49).  Throws
+// std::runtime_error on malformed input.
+void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostTree>* trees);
+
 }  // namespace lgb

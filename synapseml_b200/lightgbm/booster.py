@@ -1,6 +1,7 @@
 """LightGBMBooster: mirror of lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala
 (training subset: create :241, updateOneIteration :355-365, resetParameter :316-323, saveToString :272-278,
-getPredict :331-350, free :155) and TrainUtils.createBooster (TrainUtils.scala:16-29)."""
+getPredict :331-350, free :155), its scoring side (model string constructor :41-49, score / predictLeaf :407-427, 520-557) and
+TrainUtils.createBooster (TrainUtils.scala:16-29)."""
 import ctypes as C
 
 import numpy as np
@@ -18,6 +19,43 @@ class LightGBMBooster:
             validate(lightgbmlib().LGBM_BoosterCreate(training_dataset.dataset_ptr, parameters.encode(), C.byref(h)), "Booster")
             self.booster_handle = h
             self._train_rows = training_dataset.num_data()
+        elif model_str is not None:
+            # LightGBMBooster(modelStr): the booster is rebuilt from the model string where it is needed (:41-49)
+            h, n_iter = C.c_void_p(), C.c_int()
+            validate(lightgbmlib().LGBM_BoosterLoadModelFromString(model_str.encode(), C.byref(n_iter), C.byref(h)), "Booster LoadFromString")
+            self.booster_handle = h
+            self.num_iterations = n_iter.value
+
+    # predict_type constants of the C API (C_API_PREDICT_NORMAL / RAW_SCORE / LEAF_INDEX)
+    PREDICT_NORMAL, PREDICT_RAW, PREDICT_LEAF = 0, 1, 2
+
+    def predict_for_mat(self, features, predict_type=0, start_iteration=0, num_iteration=-1):
+        """Batch scoring on the GPU: one LGBM_BoosterPredictForMat call for all rows."""
+        lib = lightgbmlib()
+        x = np.ascontiguousarray(features, dtype=np.float64)
+        if x.ndim == 1:
+            x = x.reshape(1, -1)
+        n, ncol = x.shape
+        need = C.c_int64()
+        validate(lib.LGBM_BoosterCalcNumPredict(self.booster_handle, C.c_int(n), C.c_int(predict_type), C.c_int(start_iteration),
+                                                C.c_int(num_iteration), C.byref(need)), "Booster CalcNumPredict")
+        out = np.zeros(max(need.value, 1), dtype=np.float64)
+        out_len = C.c_int64()
+        validate(lib.LGBM_BoosterPredictForMat(self.booster_handle, x.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(n), C.c_int32(ncol),
+                                               C.c_int(1), C.c_int(predict_type), C.c_int(start_iteration), C.c_int(num_iteration),
+                                               b"", C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
+        out = out[:out_len.value]
+        return out.reshape(n, -1) if predict_type == self.PREDICT_LEAF else out
+
+    def score(self, row, raw=False):
+        """score (:407-427 -> predictForMat :520-557): one row through LGBM_BoosterPredictForMatSingleRow."""
+        lib = lightgbmlib()
+        x = np.ascontiguousarray(row, dtype=np.float64).reshape(-1)
+        out, out_len = np.zeros(1), C.c_int64()
+        validate(lib.LGBM_BoosterPredictForMatSingleRow(self.booster_handle, x.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int(len(x)), C.c_int(1),
+                                                        C.c_int(self.PREDICT_RAW if raw else self.PREDICT_NORMAL), C.c_int(0), C.c_int(-1), b"",
+                                                        C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
+        return float(out[0])
 
     def update_one_iteration(self):
         fin = C.c_int()

@@ -10,6 +10,7 @@ import numpy as np
 
 from . import network_manager as nm
 from .dataset import ReferenceDatasetUtils
+from .booster import LightGBMBooster
 from .model_text import TextModel
 from .params import (CategoricalParams, ClassifierTrainParams, DartModeParams, DatasetParams, ExecutionParams, GeneralParams,
                      ObjectiveParams, QuantizedGradParams, RankerTrainParams, RegressorTrainParams, SeedParams,
@@ -235,9 +236,25 @@ class LightGBMBase:
 
 
 class LightGBMModelBase:
+    """LightGBMModelMethods / the *Model classes: holds the model string; scoring rebuilds a native booster from it on first use
+    (LightGBMBooster.scala:41-49) and predicts on the GPU through LGBM_BoosterPredictForMat."""
+
     def __init__(self, model_str):
         self.model_str = model_str
-        self._model = TextModel(model_str)
+        self._model = TextModel(model_str)       # parsed text: feature importances only
+        self._booster = None
+
+    def _native(self):
+        if self._booster is None:
+            self._booster = LightGBMBooster(model_str=self.model_str)
+        return self._booster
+
+    def __del__(self):
+        try:
+            if self._booster is not None:
+                self._booster.free_native_memory()
+        except Exception:  # noqa: BLE001
+            pass
 
     def getNativeModel(self):
         return self.model_str
@@ -247,7 +264,10 @@ class LightGBMModelBase:
             f.write(self.model_str)
 
     def predict_raw(self, features):
-        return self._model.predict_raw(features)
+        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_RAW)
+
+    def predict_leaf(self, features):
+        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
 
     def getFeatureImportances(self, importance_type="split"):
         imp = np.zeros(self._model.max_feature_idx + 1)
@@ -261,7 +281,7 @@ class LightGBMModelBase:
 class LightGBMClassificationModel(LightGBMModelBase):
     def transform(self, features):
         raw = self.predict_raw(features)
-        p = 1.0 / (1.0 + np.exp(-raw))
+        p = self._native().predict_for_mat(features, LightGBMBooster.PREDICT_NORMAL)
         # binary: the native value is the positive-class score; expanded as the reference does (LightGBMBooster.scala:559-575)
         return dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1), prediction=(p > 0.5).astype(np.float64))
 

@@ -1,0 +1,43 @@
+"""Model string loader / writer through the C ABI without a GPU: LGBM_BoosterLoadModelFromString parses
+what LGBM_BoosterSaveModelToString writes, and writing it again gives the same text."""
+import ctypes as C
+import os
+
+import pytest
+
+from helpers import strip_parameters
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _save(native, h):
+    size = 1 << 22
+    buf = C.create_string_buffer(size)
+    n = C.c_int64()
+    assert native.LGBM_BoosterSaveModelToString(h, 0, -1, 0, C.c_int64(size), C.byref(n), buf) == 0
+    assert n.value <= size
+    return buf.value.decode()
+
+
+def test_load_then_save_reproduces_the_golden_model(native):
+    text = open(os.path.join(GOLDEN, "quant_model.txt")).read()
+    h, it = C.c_void_p(), C.c_int()
+    assert native.LGBM_BoosterLoadModelFromString(text.encode(), C.byref(it), C.byref(h)) == 0, native.LGBM_GetLastError()
+    assert it.value == text.count("Tree=")
+    for fn, want in [(native.LGBM_BoosterNumberOfTotalModel, it.value), (native.LGBM_BoosterGetNumFeature, 28), (native.LGBM_BoosterGetNumClasses, 1)]:
+        out = C.c_int()
+        assert fn(h, C.byref(out)) == 0 and out.value == want
+    assert strip_parameters(_save(native, h)) == text
+    # a loaded booster cannot train
+    fin = C.c_int()
+    assert native.LGBM_BoosterUpdateOneIter(h, C.byref(fin)) == -1
+    assert b"only predict" in native.LGBM_GetLastError()
+    assert native.LGBM_BoosterFree(h) == 0
+
+
+@pytest.mark.parametrize("bad", ["", "not a model", "tree\nnum_class=3\n", "tree\nmax_feature_idx=1\nTree=0\nnum_leaves=2\nsplit_feature=5\n",
+                                 "tree\nmax_feature_idx=1\nTree=0\nnum_leaves=2\nnum_cat=1\n"])
+def test_malformed_model_strings_are_rejected(native, bad):
+    h, it = C.c_void_p(), C.c_int()
+    assert native.LGBM_BoosterLoadModelFromString(bad.encode(), C.byref(it), C.byref(h)) == -1
+    assert len(native.LGBM_GetLastError()) > 0
