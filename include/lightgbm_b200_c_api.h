@@ -145,6 +145,18 @@ int LGBM_B200_BoosterTimerStart(BoosterHandle handle);
 int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms);
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
 
+/* ---- validation data and metrics: what early stopping evaluates every iteration
+ * (LGBM/TrainUtils.scala:137-169 through LGBM/booster/LightGBMBooster.scala:283-314; the validation dataset is created from the
+ * training dataset's bin mappers, LGBM/StreamingPartitionTask.scala:154-171).  AddValidData must precede the first iteration.
+ * data_idx 0 = training data, i >= 1 = i-th validation set.  Metrics: binary_logloss, binary_error, auc, l2, rmse, ndcg@k
+ * (`metric=` list, default by objective; `eval_at` for ndcg).  Device reductions with a fixed order; values are local to the
+ * process. */
+int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data);
+int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len);
+int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len, size_t* out_buffer_len,
+                             char** out_strs);
+int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results);
+
 /* ---- scoring.  Prediction runs on the GPU of the calling process (one thread per row walks the trees);
  * a booster loaded from a model string can only predict and save.
  * LoadModelFromString: LGBM/booster/LightGBMBooster.scala:41-49 (the model string is shipped to the executors and a booster is

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "lib", "lib_lightgbm.so")
-SOURCES = ["c_api.cu", "booster.cu", "dataset.cu", "noalloc.cu", "config.cc", "model.cc", "network.cc"]
+SOURCES = ["c_api.cu", "booster.cu", "booster_eval.cu", "dataset.cu", "noalloc.cu", "config.cc", "model.cc", "network.cc"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

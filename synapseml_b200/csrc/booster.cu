@@ -578,10 +578,36 @@ void Booster::UpdateScores() {
   if (obj == 1) APPLY(1); else if (obj == 2) APPLY(2); else APPLY(0);
 #undef APPLY
 #undef APPLY_ARGS
+  ApplyTreeToValidSets();
   k_bt_mark_applied<<<1, 1, 0, stream_>>>(d_ctrl_);
   LGB_CUDA(cudaGetLastError());
   grad_ready_ = obj != 0;
   launches_ += 2;
+}
+
+// Validation scores advance with the training scores: the same tree walk over the validation set's row records (scores only).
+void Booster::ApplyTreeToValidSets() {
+  for (ValidSet& v : valids_) {
+    const Dataset* d = v.ds;
+    const int n = static_cast<int>(d->num_data);
+    if (n == 0) continue;
+    const BinLayout& lay = d->layout;
+    const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
+#define APPLY_V(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p, \
+        nullptr, nullptr, nullptr, nullptr, tree_dev_, ds_->d_fmeta.p, d_ctrl_, cfg_.learning_rate, n, cfg_.sigmoid, 1.0, 1.0)
+    if (lay.rm_stride == 32) APPLY_V(8); else if (lay.rm_stride == 64) APPLY_V(16); else APPLY_V(0);
+#undef APPLY_V
+    ++launches_;
+  }
+}
+
+void Booster::AddConstantToValidSets(double v) {
+  for (ValidSet& s : valids_) {
+    const int n = static_cast<int>(s.ds->num_data);
+    if (n == 0) continue;
+    k_add_constant<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(s.score.p, n, v);
+    ++launches_;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------- GBDT
@@ -611,6 +637,7 @@ bool Booster::UpdateOneIter() {
     if (std::fabs(v) > kEps) {
       init_score = v;
       k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), v);
+      AddConstantToValidSets(v);
       ++launches_;
       LogInfo("Start training from score %lf", v);
     }
@@ -643,6 +670,7 @@ bool Booster::UpdateOneIter() {
     }
     tree.AsConstantTree(output);
     k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), output);
+    AddConstantToValidSets(output);
     ++launches_;
   }
   // per-iteration histogram timing (only when enabled by the bench / tests)
@@ -797,8 +825,8 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   const size_t esz = data_type == 1 ? sizeof(double) : sizeof(float);
   // row-major input is processed in chunks of rows; column-major input in one piece
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
-  dp_in_.Alloc(static_cast<size_t>(chunk_rows) * ncol * esz);
-  dp_out_.Alloc(static_cast<size_t>(chunk_rows) * per_row);
+  dp_in_.Reserve(static_cast<size_t>(chunk_rows) * ncol * esz);
+  dp_out_.Reserve(static_cast<size_t>(chunk_rows) * per_row);
   const int sig_on = obj_ == kBinary ? 1 : 0;
   for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
     const int64_t nr = std::min(chunk_rows, nrow - r0);

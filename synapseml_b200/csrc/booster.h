@@ -3,6 +3,7 @@
 // behind LGBM_BoosterCreate (lightgbm/.../booster/LightGBMBooster.scala:241, via TrainUtils.scala:16-29) and
 // LGBM_BoosterUpdateOneIter (LightGBMBooster.scala:355-365, driven by TrainUtils.scala:98-135) lives here.
 #pragma once
+#include <deque>
 #include <memory>
 #include <string>
 #include <vector>
@@ -84,6 +85,10 @@ class Booster {
   int64_t CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const;
   int NumTotalFeatures() const;
   bool predict_only() const { return predict_only_; }
+  // validation data and metrics (booster_eval.cu): data_idx 0 = training data, i >= 1 = the i-th validation set
+  void AddValidData(Dataset* valid);
+  std::vector<std::string> EvalNames();
+  void Eval(int data_idx, std::vector<double>* out);
   const Dataset* train() const { return ds_; }
 
   // Kernel-level hooks used by parity tests, bench.py's roofline measurement and the profiler (no host sync inside):
@@ -126,6 +131,25 @@ class Booster {
   DevBuf<signed char> dp_dt_;
   DevBuf<unsigned char> dp_in_;
   void UploadModel();
+  struct ValidSet {
+    Dataset* ds = nullptr;
+    DevBuf<double> score;
+    DevBuf<double> inv_max_dcg, qweight;     // ndcg: [nq][K], [nq]
+    bool ndcg_ready = false;
+  };
+  std::deque<ValidSet> valids_;
+  ValidSet train_eval_;                      // metric constants of the training data (its scores are d_score_)
+  struct MetricSpec { int kind; std::string name; };   // kind: 0 logloss, 1 error, 2 l2, 3 rmse, 4 auc, 5 ndcg (one name per eval_at)
+  std::vector<MetricSpec> metrics_;
+  bool metrics_ready_ = false;
+  void InitMetrics();
+  void PrepareNdcg(ValidSet* v, const Dataset* ds);
+  void ApplyTreeToValidSets();
+  void AddConstantToValidSets(double v);
+  DevBuf<double2> d_mpart_;
+  DevBuf<double> d_mout_, d_auc_keys_[2], d_auc_pos_, d_auc_neg_, d_auc_prefix_, d_ndcg_;
+  DevBuf<int> d_auc_idx_[2];
+  DevBuf<unsigned char> d_cub_tmp_;
   void TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const;
 
   // device state

@@ -354,6 +354,43 @@ int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_
   API_END();
 }
 
+// ---- validation data + metrics
+int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->AddValidData(static_cast<Dataset*>(const_cast<void*>(valid_data)));
+  API_END();
+}
+int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len) {
+  API_BEGIN();
+  *out_len = static_cast<int>(static_cast<Booster*>(handle)->EvalNames().size());
+  API_END();
+}
+int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len, size_t* out_buffer_len,
+                             char** out_strs) {
+  API_BEGIN();
+  const std::vector<std::string> names = static_cast<Booster*>(handle)->EvalNames();
+  *out_len = static_cast<int>(names.size());
+  size_t need = 0;
+  for (size_t i = 0; i < names.size(); ++i) {
+    need = std::max(need, names[i].size() + 1);
+    if (static_cast<int>(i) < len && out_strs != nullptr && buffer_len > 0) {
+      const size_t c = std::min(names[i].size(), buffer_len - 1);
+      memcpy(out_strs[i], names[i].data(), c);
+      out_strs[i][c] = '\0';
+    }
+  }
+  *out_buffer_len = need;
+  API_END();
+}
+int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results) {
+  API_BEGIN();
+  std::vector<double> v;
+  static_cast<Booster*>(handle)->Eval(data_idx, &v);
+  *out_len = static_cast<int>(v.size());
+  for (size_t i = 0; i < v.size(); ++i) out_results[i] = v[i];
+  API_END();
+}
+
 // ---- scoring
 int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out) {
   API_BEGIN();

@@ -1,0 +1,168 @@
+// Evaluation metrics on device-resident scores: what LGBM_BoosterGetEval returns to
+// lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/TrainUtils.scala:137-169 (early stopping) via
+// booster/LightGBMBooster.scala:283-314.  Definitions follow upstream's metric classes (binary_metric.hpp, regression_metric.hpp,
+// rank_metric.hpp / dcg_calculator.cpp): weighted means, kEpsilon = 1e-15f clamps, AUC with tied scores grouped, NDCG with
+// gains 2^label - 1 and discounts 1 / log2(2 + rank), a query without relevant documents counting as 1.
+// All reductions are two-level with a fixed order (per-CTA partials, then one CTA), so a metric is reproducible run to run.
+#pragma once
+#include <cstdint>
+
+namespace lgb {
+
+__global__ void k_iota(int* p, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = i;
+}
+
+constexpr int kMetricBlocks = 592;
+constexpr int kMetricThreads = 256;
+
+enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2 };
+
+__device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int w = 0; w < kMetricThreads / 32; ++w) t += s_w[w];
+  return t;
+}
+
+// partial[b] = (sum loss * w, sum w) over the rows of CTA b
+__global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* __restrict__ score, const float* __restrict__ label,
+                                                                  const float* __restrict__ weight, long long n, int kind, double sigmoid,
+                                                                  double2* __restrict__ partial) {
+  __shared__ double s_w[8];
+  const double kEps = (double)1e-15f;
+  double sl = 0.0, sw = 0.0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const double s = score[i];
+    const float y = label[i];
+    const double w = weight ? static_cast<double>(weight[i]) : 1.0;
+    double loss;
+    if (kind == kMetricL2) {
+      const double d = s - static_cast<double>(y);
+      loss = d * d;
+    } else {
+      const double prob = 1.0 / (1.0 + exp(-sigmoid * s));
+      if (kind == kMetricBinaryLogloss) {
+        if (y <= 0.0f) loss = (1.0 - prob > kEps) ? -log(1.0 - prob) : -log(kEps);
+        else loss = (prob > kEps) ? -log(prob) : -log(kEps);
+      } else {
+        loss = (prob <= 0.5) ? (y > 0.0f ? 1.0 : 0.0) : (y <= 0.0f ? 1.0 : 0.0);
+      }
+    }
+    sl += loss * w; sw += w;
+  }
+  const double tl = BlockSumD(sl, s_w);
+  const double tw = BlockSumD(sw, s_w);
+  if (threadIdx.x == 0) partial[blockIdx.x] = make_double2(tl, tw);
+}
+
+// one CTA: out[0..1] = sums of the partials in index order
+__global__ void __launch_bounds__(kMetricThreads) k_metric_final(const double2* __restrict__ partial, int n, double* __restrict__ out) {
+  __shared__ double s_w[8];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { a += partial[i].x; b += partial[i].y; }
+  const double ta = BlockSumD(a, s_w);
+  const double tb = BlockSumD(b, s_w);
+  if (threadIdx.x == 0) { out[0] = ta; out[1] = tb; }
+}
+
+// ---- AUC.  Rows sorted by score, descending (keys) with their original index (order).
+__global__ void k_auc_gather(const int* __restrict__ order, const float* __restrict__ label, const float* __restrict__ weight, long long n,
+                             double* __restrict__ pos_w, double* __restrict__ neg_w) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = order[i];
+    const double w = weight ? static_cast<double>(weight[r]) : 1.0;
+    const bool pos = label[r] > 0.0f;
+    pos_w[i] = pos ? w : 0.0;
+    neg_w[i] = pos ? 0.0 : w;
+  }
+}
+// pos_prefix: inclusive prefix sum of pos_w.  Every negative row contributes its weight times (positives ranked strictly
+// above its score group + half of the positives inside the group) — upstream's accumulation, written per row.
+__global__ void __launch_bounds__(kMetricThreads) k_auc_accumulate(const double* __restrict__ keys, const double* __restrict__ pos_prefix,
+                                                                    const double* __restrict__ neg_w, long long n,
+                                                                    double2* __restrict__ partial) {
+  __shared__ double s_w[8];
+  double acc = 0.0, negs = 0.0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const double nw = neg_w[i];
+    negs += nw;
+    if (nw == 0.0) continue;
+    const double k = keys[i];
+    // keys are descending: first index with key == k, last index with key == k
+    long long lo = 0, hi = i;
+    while (lo < hi) { const long long m = (lo + hi) >> 1; if (keys[m] > k) lo = m + 1; else hi = m; }
+    const long long first = lo;
+    lo = i; hi = n - 1;
+    while (lo < hi) { const long long m = (lo + hi + 1) >> 1; if (keys[m] < k) hi = m - 1; else lo = m; }
+    const long long last = lo;
+    const double before = first > 0 ? pos_prefix[first - 1] : 0.0;
+    const double in_group = pos_prefix[last] - before;
+    acc += nw * (before + 0.5 * in_group);
+  }
+  const double ta = BlockSumD(acc, s_w);
+  const double tn = BlockSumD(negs, s_w);
+  if (threadIdx.x == 0) partial[blockIdx.x] = make_double2(ta, tn);
+}
+
+// ---- NDCG@k.  One CTA per query; rank by counting (= std::stable_sort by score, descending).  out[q * K + j] = DCG@eval_at[j].
+constexpr int kMaxEvalAt = 8;
+struct NdcgArgs {
+  const double* score; const float* label; const int* qb; const double* label_gain; int num_gain;
+  int eval_at[kMaxEvalAt]; int K; int max_cnt;
+  double* dcg;      // [nq][K]
+};
+__global__ void __launch_bounds__(kMetricThreads) k_ndcg(NdcgArgs a) {
+  extern __shared__ __align__(16) unsigned char nd_smem[];
+  double* s_score = reinterpret_cast<double*>(nd_smem);
+  __shared__ double s_w[8];
+  const int q = blockIdx.x;
+  const int start = a.qb[q], cnt = a.qb[q + 1] - start;
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) s_score[d] = a.score[start + d];
+  __syncthreads();
+  double part[kMaxEvalAt];
+  #pragma unroll
+  for (int j = 0; j < kMaxEvalAt; ++j) part[j] = 0.0;
+  const int kmax = a.eval_at[a.K - 1];
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+    const double sd = s_score[d];
+    int rank = 0;
+    for (int e = 0; e < cnt; ++e) {
+      const double se = s_score[e];
+      rank += (se > sd) || (se == sd && e < d);
+    }
+    if (rank < kmax) {
+      const int lab = static_cast<int>(a.label[start + d]);
+      const double g = (lab >= 0 && lab < a.num_gain) ? a.label_gain[lab] : 0.0;
+      const double term = g / log2(2.0 + rank);
+      #pragma unroll
+      for (int j = 0; j < kMaxEvalAt; ++j)
+        if (j < a.K && rank < a.eval_at[j]) part[j] += term;
+    }
+  }
+  for (int j = 0; j < a.K; ++j) {
+    const double t = BlockSumD(part[j], s_w);
+    if (threadIdx.x == 0) a.dcg[static_cast<size_t>(q) * a.K + j] = t;
+  }
+}
+// out[j] = sum_q w_q * (max_dcg > 0 ? dcg / max_dcg : 1), out[K] = sum_q w_q; one CTA, fixed order
+__global__ void __launch_bounds__(kMetricThreads) k_ndcg_final(const double* __restrict__ dcg, const double* __restrict__ inv_max_dcg,
+                                                                const double* __restrict__ qweight, int nq, int K, double* __restrict__ out) {
+  __shared__ double s_w[8];
+  for (int j = 0; j <= K; ++j) {
+    double acc = 0.0;
+    for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+      const double w = qweight ? qweight[q] : 1.0;
+      if (j == K) { acc += w; continue; }
+      const double inv = inv_max_dcg[static_cast<size_t>(q) * K + j];
+      acc += w * (inv > 0.0 ? dcg[static_cast<size_t>(q) * K + j] * inv : 1.0);
+    }
+    const double t = BlockSumD(acc, s_w);
+    if (threadIdx.x == 0) out[j] = t;
+  }
+}
+
+}  // namespace lgb

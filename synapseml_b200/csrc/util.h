@@ -71,6 +71,7 @@ struct DevBuf {
     n = count;
     if (count) LGB_CUDA(cudaMalloc(&p, count * sizeof(T)));
   }
+  void Reserve(size_t count) { if (n < count) Alloc(count); }      // grow-only: keeps the buffer between calls
   void AllocZero(size_t count) {
     Alloc(count);
     if (count) LGB_CUDA(cudaMemset(p, 0, count * sizeof(T)));

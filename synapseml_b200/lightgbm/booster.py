@@ -80,6 +80,30 @@ class LightGBMBooster:
                 return buf.value.decode()
             size = out_len.value
 
+    def add_valid_data(self, dataset):
+        """LGBM_BoosterAddValidData (BasePartitionTask.scala: the validation dataset is attached before training starts)."""
+        validate(lightgbmlib().LGBM_BoosterAddValidData(self.booster_handle, dataset.dataset_ptr), "Add Validation Dataset")
+
+    def get_eval_names(self):
+        """getEvalNames (:283-297)."""
+        lib = lightgbmlib()
+        n = C.c_int()
+        validate(lib.LGBM_BoosterGetEvalCounts(self.booster_handle, C.byref(n)), "Booster Get Eval Counts")
+        bufs = [C.create_string_buffer(256) for _ in range(n.value)]
+        arr = (C.c_char_p * max(n.value, 1))(*[C.cast(b, C.c_char_p) for b in bufs])
+        out_n, need = C.c_int(), C.c_size_t()
+        validate(lib.LGBM_BoosterGetEvalNames(self.booster_handle, C.c_int(n.value), C.byref(out_n), C.c_size_t(256), C.byref(need), arr),
+                 "Booster Get Eval Names")
+        return [b.value.decode() for b in bufs[:out_n.value]]
+
+    def get_eval_results(self, eval_names, data_index):
+        """getEvalResults (:300-314): [(name, value)] for data_index 0 (training data) or i (i-th validation set)."""
+        out = np.zeros(max(len(eval_names), 1), dtype=np.float64)
+        n = C.c_int()
+        validate(lightgbmlib().LGBM_BoosterGetEval(self.booster_handle, C.c_int(data_index), C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))),
+                 "Booster Get Eval Results for data index: %d" % data_index)
+        return list(zip(eval_names, out[:len(eval_names)].tolist()))
+
     def inner_predict(self, data_index=0):
         lib = lightgbmlib()
         out_len = C.c_int64()

@@ -42,6 +42,20 @@ class LocalDataFrame:
         return sum(len(p["label"]) for p in self.partitions)
 
 
+def _split_validation(df, vcol):
+    train_parts, valid_parts = [], []
+    for p in df.partitions:
+        mask = np.asarray(p[vcol]).astype(bool)
+        keep = ~mask
+        train_parts.append({k: (v[keep] if k != vcol else v[keep]) for k, v in p.items() if k != vcol})
+        if mask.any():
+            valid_parts.append({k: v[mask] for k, v in p.items() if k != vcol})
+    if not valid_parts:
+        return LocalDataFrame(train_parts), None
+    keys = valid_parts[0].keys()
+    return LocalDataFrame(train_parts), {k: np.concatenate([vp[k] for vp in valid_parts]) for k in keys}
+
+
 # name -> default.  None = "not set": the key is then omitted from the native string and the native default applies
 # (LightGBMBase.scala:249-288 uses get(param), which ignores Spark-side defaults).
 _DEFAULTS = dict(
@@ -54,7 +68,7 @@ _DEFAULTS = dict(
     passThroughArgs=None, numThreads=None, dataTransferMode="streaming", samplingMode="subset", samplingSubsetSize=1000000,
     microBatchSize=100, useSingleDatasetMode=True, maxStreamingOMPThreads=16, chunkSize=10000, matrixType="auto",
     labelCol="label", featuresCol="features", weightCol=None, initScoreCol=None, slotNames=None, referenceDataset=None,
-    useQuantizedGrad=None, numGradQuantBins=None, stochasticRounding=None, isProvideTrainingMetric=None, delegate=None,
+    useQuantizedGrad=None, numGradQuantBins=None, stochasticRounding=None, isProvideTrainingMetric=None, delegate=None, validationIndicatorCol=None,
     defaultListenPort=nm.DEFAULT_LOCAL_LISTEN_PORT, timeout=1200.0, modelString=None,
 )
 _SPARK_DEFAULTS = dict(maxBin=255, binSampleCount=200000, minDataInLeaf=20, numLeaves=31)   # values getXxx returns when unset
@@ -172,6 +186,11 @@ class LightGBMBase:
         g = self._p
         t_start = time.time()
         df = self.preprocess_data(df)
+        validation_data = None
+        vcol = g.get("validationIndicatorCol")
+        if vcol:
+            # LightGBMBase.scala: rows flagged by validationIndicatorCol are collected and broadcast; training uses the rest
+            df, validation_data = _split_validation(df, vcol)
         dist_on = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
         rank = dist.get_rank() if dist_on else 0
         world = dist.get_world_size() if dist_on else 1
@@ -197,7 +216,7 @@ class LightGBMBase:
                    measures=measures, hist_timing=getattr(self, "_hist_timing", False), keep_scores=getattr(self, "_keep_scores", False),
                    # one pushing thread per partition, as Spark runs one task thread per partition on an executor
                    # (BasePartitionTask.scala:84-112); the native push is thread-safe for distinct tid
-                   threaded_push=getattr(self, "_threaded_push", True))
+                   threaded_push=getattr(self, "_threaded_push", True), validation_data=validation_data)
         if g["dataTransferMode"] == "streaming":
             serialized = g["referenceDataset"]
             if serialized is None:
@@ -222,6 +241,7 @@ class LightGBMBase:
         measures["trainingTime"] = time.time() - t0
         measures["totalTime"] = time.time() - t_start
         self.performance_measures = measures
+        self.best_iteration = measures.get("bestIteration")
         if dist_on:
             payload = [model_str]
             dist.broadcast_object_list(payload, src=0)

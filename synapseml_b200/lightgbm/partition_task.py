@@ -40,6 +40,7 @@ class BasePartitionTask:
         if info is not None:
             nm.init_lightgbm_network(info)
         booster = None
+        valid_ds = None
         try:
             dataset.validate_dataset()
             if ctx.get("feature_names"):
@@ -47,13 +48,19 @@ class BasePartitionTask:
             t0 = time.time()
             booster = train_utils.create_booster(ctx["train_params"], dataset)
             measures["boosterCreationTime"] = time.time() - t0
+            if ctx.get("validation_data") is not None:
+                valid_ds = self.generate_validation_dataset(ctx["validation_data"], dataset)
+                booster.add_valid_data(valid_ds)
             if ctx.get("hist_timing"):
                 booster.set_hist_timing(True)
-            train_utils.execute_training_iterations(ctx["train_params"], booster, measures)
+            best_iteration = train_utils.execute_training_iterations(ctx["train_params"], booster, measures, valid_ds is not None)
+            measures["bestIteration"] = best_iteration
             measures.update(booster.stats())
             # only the main worker of rank 0 returns the model (BasePartitionTask.getPartitionTaskResult :450-461)
             t0 = time.time()
-            model_str = booster.save_to_string() if (info is None or info.rank == 0) else None
+            # saveToString(bestIterationResult): iterations up to and including the best one (LightGBMBooster.scala:272-278)
+            upper = None if best_iteration is None else best_iteration + 1
+            model_str = booster.save_to_string(upper) if (info is None or info.rank == 0) else None
             measures["saveModelTime"] = time.time() - t0
             if ctx.get("keep_scores"):
                 measures["train_scores"] = booster.inner_predict(0)
@@ -61,12 +68,27 @@ class BasePartitionTask:
         finally:
             if booster is not None:
                 booster.free_native_memory()
+            if valid_ds is not None:
+                valid_ds.close()
             dataset.close()
             if info is not None and info.world > 1:
                 nm.free_lightgbm_network()
 
 
 class StreamingPartitionTask(BasePartitionTask):
+    def generate_validation_dataset(self, vdata, train_dataset):
+        """generateOptValidationDataset (StreamingPartitionTask.scala:154-171): a dataset with the training bin mappers, filled from
+        the broadcast validation rows in one go and finished."""
+        ctx = self.ctx
+        n = len(vdata["label"])
+        has_w, has_i, has_g = "weight" in vdata, "initScore" in vdata, "group" in vdata
+        handle = ReferenceDatasetUtils.get_initialized_reference_dataset(ctx["serialized_reference"], n, 1, ctx["dataset_params"],
+                                                                         has_w, has_i, has_g, 1)
+        mb = int(ctx["train_params"].executionParams.microBatchSize)
+        self.insert_rows_into_training_dataset(handle, vdata, 0, mb, 0, GroupIdManager(), has_w, has_i, has_g)
+        validate(lightgbmlib().LGBM_DatasetMarkFinished(handle), "Dataset mark finished")
+        return LightGBMDataset(handle)
+
     def prepare_dataset(self, partitions):
         ctx = self.ctx
         n_rows = sum(len(p["label"]) for p in partitions)
@@ -129,6 +151,10 @@ class StreamingPartitionTask(BasePartitionTask):
 
 
 class BulkPartitionTask(BasePartitionTask):
+    def generate_validation_dataset(self, vdata, train_dataset):
+        raise NotImplementedError("validation data in bulk mode (LGBM_DatasetCreateFromMat with a reference) is not built yet; "
+                                  "use dataTransferMode=streaming")
+
     def prepare_dataset(self, partitions):
         """DenseAggregatedColumns.generateDataset (DatasetAggregator.scala:405-429): one LGBM_DatasetCreateFromMat, then
         label / weight / init_score / group through LGBM_DatasetSetField (LightGBMDataset.scala:110-176)."""
