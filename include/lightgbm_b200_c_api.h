@@ -69,6 +69,13 @@ int LGBM_DatasetPushRowsWithMetadata(DatasetHandle dataset, const void* data, in
                                      int32_t start_row, const float* label, const float* weight, const double* init_score,
                                      const int32_t* query, int32_t tid);
 
+/* StreamingPartitionTask.scala:258-272 — sparse micro-batches (indptr_type C_API_DTYPE_INT32 = 2 / INT64 = 3; the reference passes
+ * INT64 and float64 values).  Absent entries are 0.0.  Same threading rules as the dense push. */
+int LGBM_DatasetPushRowsByCSRWithMetadata(DatasetHandle dataset, const void* indptr, int indptr_type, const int32_t* indices,
+                                          const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t start_row,
+                                          const float* label, const float* weight, const double* init_score, const int32_t* query,
+                                          int32_t tid);
+
 /* StreamingPartitionTask.scala:358 / :143,168 */
 int LGBM_DatasetSetWaitForManualFinish(DatasetHandle dataset, int wait);
 int LGBM_DatasetMarkFinished(DatasetHandle dataset);

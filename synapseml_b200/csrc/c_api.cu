@@ -110,6 +110,16 @@ int LGBM_DatasetPushRowsWithMetadata(DatasetHandle dataset, const void* data, in
   API_END();
 }
 
+int LGBM_DatasetPushRowsByCSRWithMetadata(DatasetHandle dataset, const void* indptr, int indptr_type, const int32_t* indices,
+                                          const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t start_row,
+                                          const float* label, const float* weight, const double* init_score, const int32_t* query,
+                                          int32_t tid) {
+  API_BEGIN();
+  static_cast<Dataset*>(dataset)->PushRowsByCSR(indptr, indptr_type, indices, data, data_type, nindptr, nelem, start_row, label, weight,
+                                                init_score, query, tid);
+  API_END();
+}
+
 int LGBM_DatasetSetWaitForManualFinish(DatasetHandle dataset, int wait) {
   API_BEGIN();
   static_cast<Dataset*>(dataset)->wait_for_manual_finish = wait != 0;

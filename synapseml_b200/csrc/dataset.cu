@@ -754,6 +754,51 @@ void Dataset::PushRows(const void* data, int data_type, int32_t nrow, int32_t nc
     s->seg_rows += take;
     done += take;
   }
+  PushMetadata(nrow, start_row, lab, w, init, q);
+}
+
+// Sparse micro-batches (StreamingPartitionTask.scala:239-277): the CSR rows are expanded into the same pinned dense staging rows
+// the dense path fills (zero fill + scatter, a formatting step at memory speed), then take the dense path: H2D and the K2 binning
+// kernel.  Absent entries are 0.0, exactly what the reference's SparseVector means.
+void Dataset::PushRowsByCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data, int data_type,
+                            int64_t nindptr, int64_t nelem, int64_t start_row, const float* lab, const float* w, const double* init,
+                            const int32_t* q, int tid) {
+  LGB_CHECK(indptr_type == 2 || indptr_type == 3, "PushRowsByCSR: indptr_type must be C_API_DTYPE_INT32 or INT64");
+  LGB_CHECK(data_type == 1 || data_type == 0, "PushRowsByCSR: data_type must be C_API_DTYPE_FLOAT32 or FLOAT64");
+  const int64_t nrow = nindptr - 1;
+  const int ncol = num_total_features;
+  LGB_CHECK(nrow >= 0 && start_row >= 0 && start_row + nrow <= num_data, "PushRowsByCSR: rows [%lld, %lld) are outside the dataset (%lld rows)",
+            (long long)start_row, (long long)(start_row + nrow), (long long)num_data);
+  LGB_CHECK(!finished, "PushRowsByCSR: the dataset is already finished");
+  auto ptr_at = [&](int64_t i) -> int64_t {
+    return indptr_type == 3 ? static_cast<const int64_t*>(indptr)[i] : static_cast<int64_t>(static_cast<const int32_t*>(indptr)[i]);
+  };
+  LGB_CHECK(nrow == 0 || (ptr_at(nrow) - ptr_at(0) <= nelem && ptr_at(0) >= 0), "PushRowsByCSR: indptr does not match nelem");
+  if (tid < 0) tid = 0;
+  if (static_cast<int>(slots_.size()) <= tid) EnsureSlots(tid + 1);
+  PushSlot* s = &slots_[tid];
+  int64_t done = 0;
+  while (done < nrow) {
+    if (s->seg_rows > 0 && (start_row + done != s->seg_start + s->seg_rows || static_cast<size_t>(s->seg_rows) >= s->cap_rows)) FlushSlot(s);
+    if (s->seg_rows == 0) s->seg_start = start_row + done;
+    const int64_t take = std::min<int64_t>(nrow - done, static_cast<int64_t>(s->cap_rows) - s->seg_rows);
+    double* dst = s->pinned[s->cur] + static_cast<size_t>(s->seg_rows) * ncol;
+    memset(dst, 0, sizeof(double) * take * ncol);
+    for (int64_t r = 0; r < take; ++r) {
+      double* row = dst + static_cast<size_t>(r) * ncol;
+      for (int64_t j = ptr_at(done + r); j < ptr_at(done + r + 1); ++j) {
+        const int c = indices[j];
+        LGB_CHECK(c >= 0 && c < ncol, "PushRowsByCSR: column index %d is outside [0, %d)", c, ncol);
+        row[c] = data_type == 1 ? static_cast<const double*>(data)[j] : static_cast<double>(static_cast<const float*>(data)[j]);
+      }
+    }
+    s->seg_rows += take;
+    done += take;
+  }
+  PushMetadata(static_cast<int32_t>(nrow), start_row, lab, w, init, q);
+}
+
+void Dataset::PushMetadata(int32_t nrow, int64_t start_row, const float* lab, const float* w, const double* init, const int32_t* q) {
   if (lab) std::copy(lab, lab + nrow, label.begin() + start_row);
   if (w && has_weight) std::copy(w, w + nrow, weight.begin() + start_row);
   if (init && has_init_score) std::copy(init, init + nrow, init_score.begin() + start_row);

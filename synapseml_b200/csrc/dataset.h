@@ -99,6 +99,9 @@ class Dataset {
   void InitStreaming(bool has_w, bool has_init, bool has_q, int nclasses, int nthreads);
   void PushRows(const void* data, int data_type, int32_t nrow, int32_t ncol, int64_t start_row, const float* lab,
                 const float* w, const double* init, const int32_t* q, int tid);
+  void PushRowsByCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data, int data_type, int64_t nindptr,
+                     int64_t nelem, int64_t start_row, const float* lab, const float* w, const double* init, const int32_t* q, int tid);
+  void PushMetadata(int32_t nrow, int64_t start_row, const float* lab, const float* w, const double* init, const int32_t* q);
   void MarkFinished();
   void SetFeatureNames(const char** names, int n);
   int num_features() const { return static_cast<int>(used.size()); }

@@ -156,8 +156,9 @@ class LightGBMBase:
             for f in feats:
                 if need <= 0:
                     break
-                out.append(f[:need])
-                need -= len(out[-1])
+                part = f[:need]
+                out.append(part.toarray() if hasattr(part, "toarray") else part)      # sparse rows are sampled as dense values
+                need -= out[-1].shape[0]
             return out[0] if len(out) == 1 else np.concatenate(out)
 
         if mode == "fixed":       # df.limit(numSamples)

@@ -138,6 +138,24 @@ class StreamingPartitionTask(BasePartitionTask):
             gid = part.get("_gid")
             if gid is None:
                 gid = np.array([group_ids.get_unique_index_for_id(v) for v in np.asarray(part["group"]).tolist()], dtype=np.int32)
+        if hasattr(X, "indptr"):      # scipy CSR partition: pushSparseMicroBatches (StreamingPartitionTask.scala:239-277)
+            X = X.tocsr()
+            indptr = np.ascontiguousarray(X.indptr, dtype=np.int64)
+            indices = np.ascontiguousarray(X.indices, dtype=np.int32)
+            values = np.ascontiguousarray(X.data, dtype=np.float64)
+            for s in range(0, n, micro_batch_size):
+                e = min(n, s + micro_batch_size)
+                lo, hi = int(indptr[s]), int(indptr[e])
+                ip = indptr[s:e + 1] - lo
+                validate(lib.LGBM_DatasetPushRowsByCSRWithMetadata(
+                    handle, ip.ctypes.data_as(C.c_void_p), C.c_int(3), indices[lo:hi].ctypes.data_as(C.POINTER(C.c_int32)),
+                    values[lo:hi].ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int64(e - s + 1), C.c_int64(hi - lo), C.c_int64(start_index + s),
+                    label[s:e].ctypes.data_as(C.POINTER(C.c_float)),
+                    weight[s:e].ctypes.data_as(C.POINTER(C.c_float)) if has_w else None,
+                    init[s:e].ctypes.data_as(C.POINTER(C.c_double)) if has_i else None,
+                    gid[s:e].ctypes.data_as(C.POINTER(C.c_int32)) if has_g else None,
+                    C.c_int32(tid)), "Dataset push CSR micro-batch")
+            return
         for s in range(0, n, micro_batch_size):
             e = min(n, s + micro_batch_size)
             xb = np.ascontiguousarray(X[s:e], dtype=np.float64)

@@ -107,3 +107,18 @@ def test_unsupported_options_fail_loudly(native):
     for kw in (dict(boostingType="dart"), dict(zeroAsMissing=True), dict(maxBin=1000)):
         with pytest.raises((LightGBMNativeError, NotImplementedError)):
             LightGBMClassifier(numIterations=1, **kw).fit(df)
+
+
+def test_sparse_partitions_give_the_dense_model(native):
+    # matrixType sparse: CSR micro-batches (StreamingPartitionTask.scala:239-277) must bin exactly like the dense rows
+    import scipy.sparse as sp
+    X, y = S.higgs_shape(20000)
+    X = np.where(np.abs(X) < 0.7, 0.0, X)           # ~half zeros
+    kw = dict(numIterations=4, numLeaves=15, useQuantizedGrad=True, stochasticRounding=False, samplingMode="fixed", microBatchSize=777)
+    dense = LightGBMClassifier(**kw).fit(LocalDataFrame.from_arrays(X, y, num_partitions=3)).getNativeModel()
+    parts = LocalDataFrame.from_arrays(X, y, num_partitions=3).partitions
+    for p in parts:
+        p["features"] = sp.csr_matrix(p["features"])
+    sparse = LightGBMClassifier(**kw).fit(LocalDataFrame(parts)).getNativeModel()
+    assert sparse == dense
+
