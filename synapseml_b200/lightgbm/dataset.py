@@ -49,9 +49,13 @@ class SampledData:
 
     def __init__(self, num_rows, num_cols):
         self.num_rows, self.num_cols = num_rows, num_cols
-        self.sample_data = [np.zeros(num_rows, dtype=np.float64) for _ in range(num_cols)]
-        self.sample_indexes = [np.zeros(num_rows, dtype=np.int32) for _ in range(num_cols)]
+        # one [num_cols][num_rows] block per array: column j's buffer is row j (each pre-sized to num_rows, SampledData.scala:35-40)
+        self._data = np.zeros((num_cols, num_rows), dtype=np.float64)
+        self._idx = np.zeros((num_cols, num_rows), dtype=np.int32)
+        self.sample_data = [self._data[j] for j in range(num_cols)]
+        self.sample_indexes = [self._idx[j] for j in range(num_cols)]
         self.row_counts = np.zeros(num_cols, dtype=np.int32)
+        self._next_row = 0
 
     def push_row(self, row, index):
         """SampledData.pushRow for a dense row (SampledData.scala:43-77): zeros are skipped, NaN is kept."""
@@ -62,16 +66,35 @@ class SampledData:
             self.sample_indexes[col][k] = index
             self.row_counts[col] = k + 1
 
-    def push_rows(self, rows):
-        """Vectorised equivalent of calling push_row for rows 0..n-1 in order."""
+    def push_rows(self, rows, block=None):
+        """Equivalent of calling push_row for rows 0..n-1 in order, done in cache-sized row blocks: a block without zeros goes into all
+        columns with one transposed copy, otherwise column by column."""
         rows = np.asarray(rows, dtype=np.float64)
-        for col in range(self.num_cols):
-            c = rows[:, col]
-            nz = np.flatnonzero(c != 0.0)
-            k = self.row_counts[col]
-            self.sample_data[col][k:k + len(nz)] = c[nz]
-            self.sample_indexes[col][k:k + len(nz)] = nz
-            self.row_counts[col] = k + len(nz)
+        n = rows.shape[0]
+        base = self._next_row
+        if block is None:      # ~16 MB of doubles per block
+            block = int(min(65536, max(128, (1 << 21) // max(self.num_cols, 1))))
+        for b in range(0, n, block):
+            blk = rows[b:b + block]
+            nb = blk.shape[0]
+            nzmask = blk != 0.0
+            k0 = int(self.row_counts[0]) if self.num_cols else 0
+            if nzmask.all() and (self.row_counts == k0).all():
+                self._data[:, k0:k0 + nb] = blk.T
+                self._idx[:, k0:k0 + nb] = np.arange(base + b, base + b + nb, dtype=np.int32)
+                self.row_counts += nb
+                continue
+            blk_t = np.ascontiguousarray(blk.T)
+            mask_t = np.ascontiguousarray(nzmask.T)
+            for col in range(self.num_cols):
+                nz = np.flatnonzero(mask_t[col])
+                if len(nz) == 0:
+                    continue
+                k = int(self.row_counts[col])
+                self._data[col, k:k + len(nz)] = blk_t[col, nz]
+                self._idx[col, k:k + len(nz)] = nz + (base + b)
+                self.row_counts[col] = k + len(nz)
+        self._next_row = base + n
 
     def get_sample_data(self):
         return (C.POINTER(C.c_double) * self.num_cols)(*[a.ctypes.data_as(C.POINTER(C.c_double)) for a in self.sample_data])
