@@ -277,6 +277,16 @@ void Booster::InitObjective() {
       if (ret > 0.0) ret = 1.0f / ret;
       inv[q] = ret;
     }
+    // launch order of the gradient kernel: queries longer than short_query_len_ first (longest first), then the rest
+    {
+      std::vector<int> order(nq);
+      for (int q = 0; q < nq; ++q) order[q] = q;
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return qb[a + 1] - qb[a] > qb[b + 1] - qb[b]; });
+      n_long_queries_ = 0;
+      while (n_long_queries_ < nq && qb[order[n_long_queries_] + 1] - qb[order[n_long_queries_]] > short_query_len_) ++n_long_queries_;
+      d_query_order_.Alloc(std::max(nq, 1));
+      LGB_CUDA(cudaMemcpy(d_query_order_.p, order.data(), sizeof(int) * nq, cudaMemcpyHostToDevice));
+    }
     const size_t bins = 1024 * 1024;
     min_sigmoid_input_ = -50.0 / cfg_.sigmoid / 2;
     max_sigmoid_input_ = -min_sigmoid_input_;
@@ -325,12 +335,19 @@ void Booster::ComputeGradients() {
     a.grad = d_grad_[grad_cur_].p; a.hess = d_hess_[grad_cur_].p; a.sigmoid = cfg_.sigmoid; a.min_sigmoid_input = min_sigmoid_input_;
     a.max_sigmoid_input = max_sigmoid_input_; a.idx_factor = sigmoid_table_idx_factor_;
     a.truncation_level = cfg_.lambdarank_truncation_level; a.norm = cfg_.lambdarank_norm; a.table_size = 1024 * 1024;
-    a.max_cnt = max_query_len_;
-    const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
-    const size_t smem = static_cast<size_t>(max_query_len_) * (3 * sizeof(double) + 3 * sizeof(float) + sizeof(int) + 1) + 16;
+    auto smem_for = [](int max_cnt) { return static_cast<size_t>(max_cnt) * (2 * sizeof(double) + 5 * sizeof(float) + sizeof(int)) + 16; };
     static size_t smem_set = 0;
-    if (smem > smem_set) { SetSmem(k_grad_lambdarank, smem); smem_set = smem; }
-    k_grad_lambdarank<<<nq, 256, smem, stream_>>>(a);
+    if (smem_for(max_query_len_) > smem_set) { smem_set = smem_for(max_query_len_); SetSmem(k_grad_lambdarank, smem_set); }
+    // long queries first (they are the tail), then the short ones with a small shared-memory footprint (more CTAs per SM)
+    if (n_long_queries_ > 0) {
+      a.max_cnt = max_query_len_; a.qlist = d_query_order_.p;
+      k_grad_lambdarank<<<n_long_queries_, 256, smem_for(max_query_len_), stream_>>>(a);
+    }
+    const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
+    if (nq > n_long_queries_) {
+      a.max_cnt = short_query_len_; a.qlist = d_query_order_.p + n_long_queries_;
+      k_grad_lambdarank<<<nq - n_long_queries_, 256, smem_for(short_query_len_), stream_>>>(a);
+    }
   }
   LGB_CUDA(cudaGetLastError());
   ++launches_;

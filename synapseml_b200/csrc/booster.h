@@ -178,6 +178,8 @@ class Booster {
   DevBuf<double> d_sigmoid_table_, d_inv_max_dcg_, d_label_gain_, d_discount_;
   double min_sigmoid_input_ = -50, max_sigmoid_input_ = 50, sigmoid_table_idx_factor_ = 1;
   int max_query_len_ = 0;
+  int short_query_len_ = 256, n_long_queries_ = 0;      // lambdarank launches are split by query length
+  DevBuf<int> d_query_order_;
 
   // measurement
   bool time_hist_ = false;

@@ -79,6 +79,8 @@ struct LambdarankArgs {
   float* grad; float* hess;
   double sigmoid, min_sigmoid_input, max_sigmoid_input, idx_factor;
   int truncation_level, norm, table_size, max_cnt;
+  const int* qlist;      // queries of this launch (nullptr: query = blockIdx.x); launches are split by query size so that short
+                         // queries do not pay for the shared memory of the longest one
 };
 
 __device__ __forceinline__ double LrSigmoid(const LambdarankArgs& a, double s) {
@@ -117,17 +119,17 @@ __device__ __forceinline__ bool LrPair(const LambdarankArgs& a, const double* s_
 // sum of lambdas for the normalisation walks the same row on another thread.
 __global__ void __launch_bounds__(256) k_grad_lambdarank(LambdarankArgs a) {
   extern __shared__ __align__(16) unsigned char lr_smem[];
-  const int q = blockIdx.x;
+  const int q = a.qlist ? a.qlist[blockIdx.x] : static_cast<int>(blockIdx.x);
   const int start = a.qb[q];
   const int cnt = a.qb[q + 1] - start;
   double* s_score = reinterpret_cast<double*>(lr_smem);                 // [max_cnt] sorted by rank
-  double* s_pl = s_score + a.max_cnt;                                   // staged row of pair lambdas
-  double* s_ph = s_pl + a.max_cnt;
-  float* s_label = reinterpret_cast<float*>(s_ph + a.max_cnt);         // [max_cnt]
+  double* s_2pl = s_score + a.max_cnt;                                  // staged row: 2 * pair lambda (0 for pairs that do not count)
+  float* s_label = reinterpret_cast<float*>(s_2pl + a.max_cnt);        // [max_cnt]
   float* s_lam = s_label + a.max_cnt;
   float* s_hes = s_lam + a.max_cnt;
-  int* s_doc = reinterpret_cast<int*>(s_hes + a.max_cnt);              // rank -> doc
-  unsigned char* s_flag = reinterpret_cast<unsigned char*>(s_doc + a.max_cnt);   // bit 0: pair counted, bit 1: i is the higher label
+  float* s_di = s_hes + a.max_cnt;                                      // staged row: the pair's signed lambda as document i sees it
+  float* s_hf = s_di + a.max_cnt;                                       // staged row: the pair's hessian
+  int* s_doc = reinterpret_cast<int*>(s_hf + a.max_cnt);               // rank -> doc
   __shared__ double s_sum;
   const double* sc = a.score + start;
   const float* lb = a.label + start;
@@ -154,34 +156,31 @@ __global__ void __launch_bounds__(256) k_grad_lambdarank(LambdarankArgs a) {
   for (int i = 0; i < imax; ++i) {
     if (s_score[i] == KMINSCORE) continue;
     for (int j = i + 1 + threadIdx.x; j < cnt; j += blockDim.x) {
-      unsigned char flag = 0;
+      float di = 0.0f, hf = 0.0f;
+      double two_pl = 0.0;
       if (s_score[j] != KMINSCORE) {
         double pl, ph; bool i_high;
         if (LrPair(a, s_score, s_label, i, j, inverse_max_dcg, norm_on, &pl, &ph, &i_high)) {
-          flag = 1 | (i_high ? 2 : 0);
-          s_pl[j] = pl; s_ph[j] = ph;
+          const float plf = static_cast<float>(pl);
+          hf = static_cast<float>(ph);
+          two_pl = 2 * pl;
+          di = i_high ? plf : -plf;
           // document j is the lower one when i is the higher one
-          s_lam[j] = i_high ? s_lam[j] - static_cast<float>(pl) : s_lam[j] + static_cast<float>(pl);
-          s_hes[j] += static_cast<float>(ph);
+          s_lam[j] = i_high ? s_lam[j] - plf : s_lam[j] + plf;
+          s_hes[j] += hf;
         }
       }
-      s_flag[j] = flag;
+      // pairs that do not count are staged as zeros: x + 0 == x, so the walks below need no branch and pipeline
+      s_di[j] = di; s_hf[j] = hf; s_2pl[j] = two_pl;
     }
     __syncthreads();
     if (threadIdx.x == (i & 31)) {               // warp 0: document i's sums over its row, in increasing j
       float lam = s_lam[i], hes = s_hes[i];
-      for (int j = i + 1; j < cnt; ++j) {
-        const unsigned char fl = s_flag[j];
-        if (!(fl & 1)) continue;
-        const float pl = static_cast<float>(s_pl[j]);
-        if (fl & 2) lam += pl; else lam -= pl;
-        hes += static_cast<float>(s_ph[j]);
-      }
+      for (int j = i + 1; j < cnt; ++j) { lam += s_di[j]; hes += s_hf[j]; }
       s_lam[i] = lam; s_hes[i] = hes;
     } else if (a.norm && threadIdx.x == 32 + (i & 31)) {   // warp 1: the double sum for the normalisation, same order
       double sum = s_sum;
-      for (int j = i + 1; j < cnt; ++j)
-        if (s_flag[j] & 1) sum -= 2 * s_pl[j];
+      for (int j = i + 1; j < cnt; ++j) sum -= s_2pl[j];
       s_sum = sum;
     }
     __syncthreads();
