@@ -23,6 +23,22 @@ namespace lgb {
 
 constexpr int kMaxBatch = 8;
 
+// Data-parallel learner, histogram exchange over peer memory (NVLink / NVSwitch) instead of an NCCL launch per round: every
+// rank's work areas and a completion flag are mapped into every other rank's address space (CUDA IPC).  The histogram kernel's
+// last CTA publishes "exchange #seq is complete" in its own flag; the split-search kernel waits until all ranks' flags reach
+// seq and then sums the ranks' bins while it loads them — integer sums, so every rank obtains the same totals whatever the
+// order.  The work areas are double-buffered by the parity of seq: a rank can be at most one exchange ahead of its slowest
+// peer (its next search waits for that peer's next histogram), so the buffer it clears for exchange seq + 2 is no longer
+// being read.  (struct PeerTable: booster.h)
+__device__ __forceinline__ unsigned int LoadAcquireSys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void StoreReleaseSys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 struct NodeDev {
   int begin, count;        // local row range (positions in index buffer `buf`; buf < 0: identity, the root)
   int buf;
@@ -208,7 +224,7 @@ __global__ void __launch_bounds__(kHistThreads, 1)
 k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,
           const int* __restrict__ idx0, const int* __restrict__ idx1, const NodeDev* __restrict__ nodes,
           BatchCtrl* __restrict__ ctrl, long long* __restrict__ work, int work_elems, int F, int rows_per_flush, int row_ctas,
-          LearnerParams P) {
+          LearnerParams P, PeerTable pt) {
   extern __shared__ unsigned int hsm_raw[];
   __shared__ HistShared sh;
   PdlLaunchDependents();
@@ -224,6 +240,15 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   __syncthreads();
   HistBody<R, BPL, FLT, ROOT>(rm, rm_stride, gh16, ghfix, idx0, idx1, nodes, ctrl, work, work_elems, F, rows_per_flush, row_ctas,
                               blockIdx.x, blockIdx.y, hsm, lane_addr, &sh, P);
+  if (pt.world > 0) {      // the CTA that finishes last tells the other ranks that this rank's histograms are complete
+    __threadfence();       // this CTA's global atomics are performed (device scope: the local L2 also serves the peers' reads) ...
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(pt.my_count, 1u) == gridDim.x * gridDim.y - 1) {
+      *pt.my_count = 0u;
+      __threadfence_system();      // ... and the last CTA publishes all of them system-wide before the flag
+      StoreReleaseSys(pt.my_flag, pt.seq);
+    }
+  }
   LGB_TRACE(ctrl, 22);
 }
 
@@ -235,7 +260,7 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
 template <bool QUANT>
 __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
                                          NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
-                                         const LearnerParams& P, int root, int f, int c, int k, int sub) {
+                                         const LearnerParams& P, int root, int f, int c, int k, int sub, const PeerTable* pt = nullptr) {
   __shared__ int s_last_all[kMaxFindSubs];
   __shared__ double s_gain_all[kMaxFindSubs][8];
   __shared__ int s_feat_all[kMaxFindSubs][8], s_idx_all[kMaxFindSubs][8];
@@ -285,12 +310,22 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
   const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
   longlong2 v;
-  if (QUANT) {     // packed work area: (sum g << 32) + sum h
-    const long long pk = work[static_cast<size_t>(root ? 0 : k) * work_elems + static_cast<size_t>(f) * kBins + b];
+  const size_t item_off = static_cast<size_t>(root ? 0 : k) * work_elems;
+  if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
+    long long a = 0, bsum = 0;
+    for (int r = 0; r < pt->world; ++r) {
+      const long long* w = pt->work[r] + pt->parity_off + item_off;
+      if (QUANT) a += w[static_cast<size_t>(f) * kBins + b];
+      else { const longlong2 t = *reinterpret_cast<const longlong2*>(w + off); a += t.x; bsum += t.y; }
+    }
+    if (QUANT) { v.y = a & 0xffffffffLL; v.x = (a - v.y) >> 32; }
+    else { v.x = a; v.y = bsum; }
+  } else if (QUANT) {     // packed work area: (sum g << 32) + sum h
+    const long long pk = work[item_off + static_cast<size_t>(f) * kBins + b];
     v.y = pk & 0xffffffffLL;
     v.x = (pk - v.y) >> 32;
   } else {
-    v = *reinterpret_cast<const longlong2*>(work + static_cast<size_t>(root ? 0 : k) * work_elems + off);
+    v = *reinterpret_cast<const longlong2*>(work + item_off + off);
   }
   bool used = true;
   if (!root) {
@@ -354,7 +389,7 @@ template <bool QUANT>
 __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
                                                  const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
                                                  BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
-                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root) {
+                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
   PdlLaunchDependents();
   LGB_TRACE(ctrl, 30);
   PdlWait();
@@ -362,7 +397,12 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   if (ctrl->done) return;
   const int k = blockIdx.z;
   if (!root && k >= ctrl->batch_n) return;
-  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, blockIdx.x, blockIdx.y, k, 0);
+  if (pt.world > 0) {      // every rank's histograms of this exchange must be complete
+    if (threadIdx.x < pt.world)
+      while (static_cast<int>(LoadAcquireSys(pt.flag[threadIdx.x]) - pt.seq) < 0) {}
+    __syncthreads();
+  }
+  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, blockIdx.x, blockIdx.y, k, 0, &pt);
   LGB_TRACE(ctrl, 32);
 }
 

@@ -110,7 +110,27 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   max_nodes_ = 1 + 2 * max_expansions;
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
   d_hist_pool_.Alloc(hist_elems * (1 + max_expansions));
-  d_hist_work_.Alloc(hist_elems * kMaxBatch);
+  d_hist_work_.Alloc(hist_elems * kMaxBatch * 2);      // two parities (only the first is used without the peer exchange)
+  work_stride_ = static_cast<long long>(hist_elems) * kMaxBatch;
+  memset(&peers_, 0, sizeof(peers_));
+  if (net_->active() && net_->world() <= kMaxPeers && (getenv("LGB_B200_PEER_EXCHANGE") == nullptr || atoi(getenv("LGB_B200_PEER_EXCHANGE")) != 0)) {
+    // histogram exchange over peer memory (batch_tree.cuh: PeerTable); falls back to NCCL all-reduce if the mapping fails
+    d_peer_flags_.AllocZero(64);
+    if (net_->ExchangePeerPointers(d_hist_work_.p, &peer_work_) && net_->ExchangePeerPointers(d_peer_flags_.p, &peer_flags_)) {
+      for (int r = 0; r < net_->world(); ++r) {
+        peers_.work[r] = static_cast<const long long*>(peer_work_[r]);
+        peers_.flag[r] = static_cast<const unsigned int*>(peer_flags_[r]);
+      }
+      peers_.my_flag = d_peer_flags_.p;
+      peers_.my_count = d_peer_flags_.p + 32;
+      peers_.world = net_->world();
+      LogInfo("Histogram exchange over peer memory (%d ranks)", peers_.world);
+      if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: exchange over peer memory, %d ranks\n", net_->rank(), peers_.world);
+    } else {
+      LogWarning("Peer memory could not be mapped; histograms are exchanged with NCCL all-reduce");
+      if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: mapping failed, NCCL fallback\n", net_->rank());
+    }
+  }
   // quantized mode packs (sum g, sum h) of a bin into one int64 (hist_kernel.cuh), float mode keeps two
   work_elems_ = static_cast<int>(lp_.quantized ? hist_elems / 2 : hist_elems);
   LGB_CHECK(!lp_.quantized || static_cast<double>(n_global_) * cfg_.num_grad_quant_bins < 4294967296.0,
@@ -172,6 +192,7 @@ Booster::~Booster() {
   cudaSetDevice(device_);
   try { ProfReport(); } catch (...) {}
   try { DumpTrace(); } catch (...) {}
+  if (peers_.world > 0) { net_->ClosePeerPointers(peer_work_); net_->ClosePeerPointers(peer_flags_); }
   if (d_nodes_) cudaFree(d_nodes_);
   if (d_ctrl_) cudaFree(d_ctrl_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
@@ -386,7 +407,10 @@ void Booster::LaunchHist(bool root) {
     rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
   }
   // non-root launches find their work areas already cleared by k_bt_part_scatter
-  if (root) LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, sizeof(long long) * work_elems_, stream_));
+  PeerTable pt = peers_;
+  if (pt.world > 0) { ++exchange_seq_; pt.seq = exchange_seq_; }
+  long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
+  if (root) LGB_CUDA(cudaMemsetAsync(work, 0, sizeof(long long) * work_elems_, stream_));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (time_hist_) {
     if (hist_events_used_ == hist_events_.size()) {
@@ -399,7 +423,7 @@ void Booster::LaunchHist(bool root) {
     LGB_CUDA(cudaEventRecord(e0, stream_));
   }
 #define LAUNCH_HIST_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, d_idx_[0].p, d_idx_[1].p, \
-                         d_nodes_, d_ctrl_, d_hist_work_.p, work_elems_, F_, rows_per_flush, row_ctas, lp_
+                         d_nodes_, d_ctrl_, work, work_elems_, F_, rows_per_flush, row_ctas, lp_, pt
 #define LAUNCH_HIST(RR, BPL, FLT)                                                                                     \
   do {                                                                                                                \
     if (root) LaunchPdl(k_bt_hist<RR, BPL, FLT, true>, grid, dim3(kHistThreads), kHistSmem, stream_, LAUNCH_HIST_ARGS);  \
@@ -417,17 +441,22 @@ void Booster::LaunchHist(bool root) {
   ++launches_;
   ++hist_kernel_launches_;
   // data-parallel learner: every rank needs the global histograms of the batch (integer sums: order-independent)
-  if (net_->active()) net_->AllReduceSumInt64(d_hist_work_.p, static_cast<size_t>(work_elems_) * (root ? 1 : max_batch_), stream_);
+  if (net_->active() && peers_.world == 0)
+    net_->AllReduceSumInt64(work, static_cast<size_t>(work_elems_) * (root ? 1 : max_batch_), stream_);
 }
 
 void Booster::LaunchFind(bool root) {
   dim3 grid(F_, root ? 1 : 2, root ? 1 : max_batch_);
+  PeerTable pt = peers_;
+  pt.seq = exchange_seq_;
+  pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
+  long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
   if (lp_.quantized)
-    LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, d_hist_work_.p, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0);
+    LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   else
-    LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, d_hist_work_.p, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0);
+    LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   ++launches_;
 }
 
@@ -485,12 +514,14 @@ void Booster::LaunchTreeKernel() {
 void Booster::EnqueueRounds(int rounds) {
   for (int r = 0; r < rounds; ++r) {
     ProfBegin("partition");
+    // the partition kernel clears the work areas the round's histograms go into: with the peer exchange that is the other parity
+    long long* next_work = d_hist_work_.p + (peers_.world > 0 ? ((exchange_seq_ + 1u) & 1u) * work_stride_ : 0);
     if (idx_es_ == 2)
       LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_hist_work_.p, work_elems_);
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
     else
       LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, d_hist_work_.p, work_elems_);
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
     ProfEnd();
     ProfBegin("hist"); LaunchHist(false); ProfEnd();
     ProfBegin("find"); LaunchFind(false); ProfEnd();

@@ -15,6 +15,18 @@
 namespace lgb {
 struct NodeDev;
 struct BatchCtrl;
+
+// Peer-memory histogram exchange of the data-parallel learner (described in batch_tree.cuh).  Passed to kernels by value.
+constexpr int kMaxPeers = 8;
+struct PeerTable {
+  const long long* work[kMaxPeers];     // every rank's work allocation (both parities), mapped into this process
+  const unsigned int* flag[kMaxPeers];  // every rank's "histograms of exchange #seq are complete" word
+  unsigned int* my_flag;
+  unsigned int* my_count;               // CTAs of the running histogram kernel that are finished
+  int world;                            // 0: no exchange (single GPU, or the NCCL fallback)
+  unsigned int seq;                     // the exchange this launch belongs to
+  long long parity_off;                 // element offset of this exchange's buffer inside a rank's work allocation
+};
 }  // namespace lgb
 
 namespace lgb {
@@ -190,6 +202,12 @@ class Booster {
   int work_elems_ = 0;
   DevBuf<long long> d_trace_;
   int trace_cap_ = 0, trace_from_ = 0;
+  // peer-memory histogram exchange (data-parallel learner)
+  PeerTable peers_;
+  std::vector<void*> peer_work_, peer_flags_;
+  DevBuf<unsigned int> d_peer_flags_;
+  unsigned int exchange_seq_ = 0;
+  long long work_stride_ = 0;
   bool use_persistent_ = false;
   size_t persist_smem_ = 0;
   int part_blocks_ = 592;                   // 4 x 148 SMs (k_bt_partition is built for 4 CTAs per SM)

@@ -244,6 +244,50 @@ void Network::HostAllReduceSum(double* vals, int n) {
   LGB_CUDA(cudaStreamSynchronize(host_stream_));
 }
 
+bool Network::ExchangePeerPointers(void* local, std::vector<void*>* peers) {
+  peers->clear();
+  if (world_ <= 1) { peers->push_back(local); return true; }
+  LGB_CUDA(cudaSetDevice(device_));
+  cudaIpcMemHandle_t mine;
+  long long words[sizeof(cudaIpcMemHandle_t) / sizeof(long long)];
+  static_assert(sizeof(cudaIpcMemHandle_t) % sizeof(long long) == 0, "handle size");
+  const bool ok_local = cudaIpcGetMemHandle(&mine, local) == cudaSuccess;
+  if (!ok_local) { cudaGetLastError(); memset(&mine, 0, sizeof(mine)); }
+  memcpy(words, &mine, sizeof(mine));
+  const int nw = static_cast<int>(sizeof(mine) / sizeof(long long));
+  std::vector<std::vector<long long>> all(nw);
+  for (int i = 0; i < nw; ++i) HostAllGatherInt64(words[i], &all[i]);
+  std::vector<long long> oks;
+  HostAllGatherInt64(ok_local ? 1 : 0, &oks);
+  bool ok = true;
+  for (long long v : oks) ok = ok && v != 0;
+  peers->assign(world_, nullptr);
+  if (ok) {
+    for (int r = 0; r < world_; ++r) {
+      if (r == rank_) { (*peers)[r] = local; continue; }
+      cudaIpcMemHandle_t h;
+      long long w[sizeof(cudaIpcMemHandle_t) / sizeof(long long)];
+      for (int i = 0; i < nw; ++i) w[i] = all[i][r];
+      memcpy(&h, w, sizeof(h));
+      void* p = nullptr;
+      if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+      (*peers)[r] = p;
+    }
+  }
+  // everybody must agree, or some ranks would wait for flags nobody writes
+  std::vector<long long> agree;
+  HostAllGatherInt64(ok ? 1 : 0, &agree);
+  bool all_ok = true;
+  for (long long v : agree) all_ok = all_ok && v != 0;
+  if (!all_ok) { ClosePeerPointers(*peers); peers->clear(); }
+  return all_ok;
+}
+
+void Network::ClosePeerPointers(const std::vector<void*>& peers) {
+  for (int r = 0; r < static_cast<int>(peers.size()); ++r)
+    if (r != rank_ && peers[r] != nullptr) cudaIpcCloseMemHandle(peers[r]);
+}
+
 void Network::HostAllGatherInt64(long long mine, std::vector<long long>* all) {
   all->assign(world_, mine);
   if (world_ <= 1) return;

@@ -31,6 +31,11 @@ class Network {
   // small host-value collectives (blocking); used at set-up time only
   void HostAllReduceSum(double* vals, int n);
   void HostAllGatherInt64(long long mine, std::vector<long long>* all);
+  // Peer-memory exchange (all ranks on one NVLink / NVSwitch node): every rank contributes one cudaMalloc'ed buffer and gets
+  // the device addresses of all ranks' buffers in its own address space (own rank: the local pointer).  Blocking, set-up time.
+  // Returns false (and leaves `peers` empty) when a peer's memory cannot be mapped; the caller then stays on NCCL.
+  bool ExchangePeerPointers(void* local, std::vector<void*>* peers);
+  void ClosePeerPointers(const std::vector<void*>& peers);
 
   // parse "h:p,h:p,..." and find this process's rank; exposed for CPU tests
   static std::vector<std::pair<std::string, int>> ParseMachines(const std::string& machines);
