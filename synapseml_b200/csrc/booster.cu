@@ -62,6 +62,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   device_ = train->device;
   LGB_CUDA(cudaSetDevice(device_));
   LGB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  LGB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+  LGB_CUDA(cudaEventCreateWithFlags(&ev_rounds_done_, cudaEventDisableTiming));
   // Histogram passes over non-root leaves gather one 32-byte row record per visited row: ask L2 not to over-fetch 64 bytes
   // per miss (the default granularity), which doubles the DRAM traffic of sparse gathers.  A hint; failure is harmless.
   if (getenv("LGB_B200_L2_FETCH_64") == nullptr) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 32);
@@ -196,6 +198,8 @@ Booster::~Booster() {
   if (d_nodes_) cudaFree(d_nodes_);
   if (d_ctrl_) cudaFree(d_ctrl_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
+  if (copy_stream_) cudaStreamDestroy(copy_stream_);
+  if (ev_rounds_done_) cudaEventDestroy(ev_rounds_done_);
   for (auto& e : hist_events_) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (timer_ev_[0]) { cudaEventDestroy(timer_ev_[0]); cudaEventDestroy(timer_ev_[1]); }
 }
@@ -544,6 +548,8 @@ void Booster::TrainTree(HostTree* out) {
   ++launches_;
   if (use_persistent_ && !time_hist_ && !prof_) {
     LaunchTreeKernel();
+    LGB_CUDA(cudaEventRecord(ev_rounds_done_, stream_));
+    UpdateScores();
     LGB_CHECK(FetchTree(out), "the persistent tree kernel returned before the tree was finished");
     return;
   }
@@ -555,6 +561,8 @@ void Booster::TrainTree(HostTree* out) {
   int total = 0;
   while (true) {
     EnqueueRounds(rounds);
+    LGB_CUDA(cudaEventRecord(ev_rounds_done_, stream_));
+    ProfBegin("score_update"); UpdateScores(); ProfEnd();      // does nothing on the device unless the tree is finished
     total += rounds;
     LGB_CUDA(cudaGetLastError());
     if (FetchTree(out)) break;
@@ -566,10 +574,13 @@ void Booster::TrainTree(HostTree* out) {
 // Copies the control block and the tree arrays back; false when the tree is not finished yet (more rounds are needed).
 bool Booster::FetchTree(HostTree* t) {
   const int L = cfg_.num_leaves;
+  // the copies wait for the tree (the event recorded behind its last round), not for the apply-tree pass enqueued after it: the
+  // host decodes the tree and enqueues the next iteration while that pass runs
   BatchCtrl hc;
-  LGB_CUDA(cudaMemcpyAsync(h_tree_blob_.data(), d_tree_blob_.p, tree_blob_bytes_, cudaMemcpyDeviceToHost, stream_));
-  LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, stream_));
-  Sync();
+  LGB_CUDA(cudaStreamWaitEvent(copy_stream_, ev_rounds_done_, 0));
+  LGB_CUDA(cudaMemcpyAsync(h_tree_blob_.data(), d_tree_blob_.p, tree_blob_bytes_, cudaMemcpyDeviceToHost, copy_stream_));
+  LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, copy_stream_));
+  LGB_CUDA(cudaStreamSynchronize(copy_stream_));
   if (!hc.done) return false;
   last_rounds_ = hc.rounds;
   rounds_total_ += hc.rounds; expansions_total_ += (hc.num_nodes - 1) / 2; splits_total_ += hc.num_leaves - 1;
@@ -700,11 +711,11 @@ bool Booster::UpdateOneIter() {
     grad_ready_ = false;
     ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
     TrainTree(&tree);
+    if (tree.num_leaves <= 1) grad_ready_ = false;      // no tree, so the apply pass did nothing
   }
   bool should_continue = false;
   if (tree.num_leaves > 1) {
-    should_continue = true;
-    ProfBegin("score_update"); UpdateScores(); ProfEnd();
+    should_continue = true;      // (the scores were advanced inside TrainTree, behind the tree's last round)
     tree.Shrinkage(cfg_.learning_rate);
     if (std::fabs(init_score) > kEps) tree.AddBias(init_score);
   } else if (models_.empty()) {

@@ -125,7 +125,8 @@ class Booster {
   Config cfg_;
   LearnerParams lp_{};
   int device_ = 0;
-  cudaStream_t stream_ = nullptr;
+  cudaStream_t stream_ = nullptr, copy_stream_ = nullptr;
+  cudaEvent_t ev_rounds_done_ = nullptr;
   Network* net_ = nullptr;
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
