@@ -914,14 +914,14 @@ void Booster::DebugRootHistogram(long long* out) {
   // out: [F][256][2] (sum g, sum h); the quantized work area is packed, one int64 per bin
   if (lp_.quantized) {
     std::vector<long long> pk(work_elems_);
-    LGB_CUDA(cudaMemcpy(pk.data(), d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
+    LGB_CUDA(cudaMemcpy(pk.data(), d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
     for (int i = 0; i < work_elems_; ++i) {
       const long long h = pk[i] & 0xffffffffLL;
       out[2 * i] = (pk[i] - h) >> 32;
       out[2 * i + 1] = h;
     }
   } else {
-    LGB_CUDA(cudaMemcpy(out, d_hist_work_.p, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
+    LGB_CUDA(cudaMemcpy(out, d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_, sizeof(long long) * work_elems_, cudaMemcpyDeviceToHost));
   }
 }
 
