@@ -173,6 +173,9 @@ int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double
  *   predict_type 0 = normal (sigmoid for binary), 1 = raw score, 2 = leaf index; 3 (feature contributions) returns -1.
  *   The single-row form costs one kernel launch and one device round trip per call: batch rows through PredictForMat. */
 int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out);
+/* LGBM/booster/LightGBMBooster.scala:501-508 (getFeatureImportances): importance_type 0 = split counts, 1 = total gains;
+ * out_results has one entry per feature (LGBM_BoosterGetNumFeature). */
+int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type, double* out_results);
 int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
                                int64_t* out_len);
 int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,

@@ -826,6 +826,20 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
 
 int Booster::NumTotalFeatures() const { return predict_only_ ? loaded_header_.max_feature_idx + 1 : ds_->num_total_features; }
 
+void Booster::FeatureImportance(int num_iteration, int importance_type, double* out) const {
+  LGB_CHECK(importance_type == 0 || importance_type == 1, "FeatureImportance: importance_type must be 0 (split) or 1 (gain)");
+  const int nf = NumTotalFeatures();
+  for (int j = 0; j < nf; ++j) out[j] = 0.0;
+  const int n = num_iteration > 0 ? std::min<int>(num_iteration, static_cast<int>(models_.size())) : static_cast<int>(models_.size());
+  for (int t = 0; t < n; ++t) {
+    const HostTree& tr = models_[t];
+    for (int k = 0; k < tr.num_leaves - 1; ++k) {
+      if (tr.split_gain[k] <= 0.0f) continue;      // upstream counts only splits with positive gain
+      out[tr.split_feature[k]] += importance_type == 0 ? 1.0 : static_cast<double>(tr.split_gain[k]);
+    }
+  }
+}
+
 void Booster::TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const {
   const int n = static_cast<int>(models_.size());
   *t0 = std::min(std::max(0, start_iteration), n);

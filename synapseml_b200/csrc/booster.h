@@ -96,6 +96,8 @@ class Booster {
                      int num_iteration, double* out, int64_t* out_len);
   int64_t CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const;
   int NumTotalFeatures() const;
+  // importance_type 0: number of splits per feature, 1: total split gain per feature; first num_iteration trees (<= 0: all)
+  void FeatureImportance(int num_iteration, int importance_type, double* out) const;
   bool predict_only() const { return predict_only_; }
   // validation data and metrics (booster_eval.cu): data_idx 0 = training data, i >= 1 = the i-th validation set
   void AddValidData(Dataset* valid);

@@ -410,6 +410,11 @@ int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iteratio
   *out = b.release();
   API_END();
 }
+int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type, double* out_results) {
+  API_BEGIN();
+  static_cast<Booster*>(handle)->FeatureImportance(num_iteration, importance_type, out_results);
+  API_END();
+}
 int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
                                int64_t* out_len) {
   API_BEGIN();

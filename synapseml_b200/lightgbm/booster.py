@@ -112,6 +112,13 @@ class LightGBMBooster:
                  "Booster get predict")
         return out[:out_len.value]
 
+    def get_feature_importances(self, importance_type="split"):
+        """getFeatureImportances (:501-508)."""
+        out = np.zeros(self.num_features(), dtype=np.float64)
+        validate(lightgbmlib().LGBM_BoosterFeatureImportance(self.booster_handle, C.c_int(-1), C.c_int(0 if importance_type == "split" else 1),
+                                                             out.ctypes.data_as(C.POINTER(C.c_double))), "Booster FeatureImportance")
+        return out.tolist()
+
     def num_total_model(self):
         out = C.c_int()
         validate(lightgbmlib().LGBM_BoosterNumberOfTotalModel(self.booster_handle, C.byref(out)), "Booster NumberOfTotalModel")

@@ -291,12 +291,7 @@ class LightGBMModelBase:
         return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
 
     def getFeatureImportances(self, importance_type="split"):
-        imp = np.zeros(self._model.max_feature_idx + 1)
-        for t in self._model.trees:
-            if t.num_leaves > 1:
-                for f, gain in zip(t.split_feature, t.split_gain):
-                    imp[f] += 1 if importance_type == "split" else gain
-        return imp.tolist()
+        return self._native().get_feature_importances(importance_type)
 
 
 class LightGBMClassificationModel(LightGBMModelBase):

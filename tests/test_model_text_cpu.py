@@ -28,6 +28,16 @@ def test_load_then_save_reproduces_the_golden_model(native):
         out = C.c_int()
         assert fn(h, C.byref(out)) == 0 and out.value == want
     assert strip_parameters(_save(native, h)) == text
+    # feature importances from the loaded trees (split counts are the model text's feature_importances block)
+    import numpy as np
+    imp = np.zeros(28)
+    assert native.LGBM_BoosterFeatureImportance(h, -1, 0, imp.ctypes.data_as(C.POINTER(C.c_double))) == 0
+    block = text.split("feature_importances:\n")[1].split("\n\n")[0].strip().splitlines()
+    want = {int(l.split("=")[0].split("_")[1]): int(l.split("=")[1]) for l in block}
+    assert {j: int(v) for j, v in enumerate(imp) if v > 0} == want
+    gain = np.zeros(28)
+    assert native.LGBM_BoosterFeatureImportance(h, -1, 1, gain.ctypes.data_as(C.POINTER(C.c_double))) == 0
+    assert (gain > 0).sum() == len(want) and gain.sum() > 0
     # a loaded booster cannot train
     fin = C.c_int()
     assert native.LGBM_BoosterUpdateOneIter(h, C.byref(fin)) == -1
