@@ -367,7 +367,9 @@ int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_
 // ---- validation data + metrics
 int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data) {
   API_BEGIN();
-  static_cast<Booster*>(handle)->AddValidData(static_cast<Dataset*>(const_cast<void*>(valid_data)));
+  Dataset* v = static_cast<Dataset*>(const_cast<void*>(valid_data));
+  if (v != nullptr && !v->finished) v->MarkFinished();     // bulk path: CreateFromMat(reference) + SetField, as for the training data
+  static_cast<Booster*>(handle)->AddValidData(v);
   API_END();
 }
 int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len) {

@@ -170,8 +170,23 @@ class StreamingPartitionTask(BasePartitionTask):
 
 class BulkPartitionTask(BasePartitionTask):
     def generate_validation_dataset(self, vdata, train_dataset):
-        raise NotImplementedError("validation data in bulk mode (LGBM_DatasetCreateFromMat with a reference) is not built yet; "
-                                  "use dataTransferMode=streaming")
+        """BulkPartitionTask.getValidationDatasetInternal (BulkPartitionTask.scala): the broadcast validation rows as one dense matrix,
+        binned with the training dataset as reference (LGBM_DatasetCreateFromMat(..., reference = train))."""
+        lib = lightgbmlib()
+        X = np.ascontiguousarray(vdata["features"].toarray() if hasattr(vdata["features"], "toarray") else vdata["features"], dtype=np.float64)
+        handle = C.c_void_p()
+        validate(lib.LGBM_DatasetCreateFromMat(X.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(X.shape[0]), C.c_int32(X.shape[1]),
+                                               C.c_int(1), self.ctx["dataset_params"].encode(), train_dataset.dataset_ptr, C.byref(handle)),
+                 "Dataset create")
+        ds = LightGBMDataset(handle)
+        ds.add_float_field(vdata["label"], "label")
+        if "weight" in vdata:
+            ds.add_float_field(vdata["weight"], "weight")
+        if "initScore" in vdata:
+            ds.add_double_field(vdata["initScore"], "init_score")
+        if "group" in vdata:
+            ds.add_group_column(np.asarray(vdata["group"]).tolist())
+        return ds
 
     def prepare_dataset(self, partitions):
         """DenseAggregatedColumns.generateDataset (DatasetAggregator.scala:405-429): one LGBM_DatasetCreateFromMat, then

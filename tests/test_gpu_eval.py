@@ -137,3 +137,18 @@ def test_early_stopping_through_the_estimator(native):
     assert int(np.argmin(vloss)) == best and len(vloss) == best + 1 + 5
     tloss = [h[0]["binary_logloss"] for h in hist if h[0] is not None]
     assert all(b < a for a, b in zip(tloss, tloss[1:]))      # training loss keeps falling
+
+
+def test_validation_metrics_are_the_same_in_bulk_and_streaming_mode(native):
+    X, y = S.higgs_shape(20000)
+    valid = np.zeros(len(y), dtype=bool)
+    valid[15000:] = True
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2, isVal=valid)
+    hist = {}
+    for mode in ("streaming", "bulk"):
+        est = LightGBMClassifier(numIterations=5, numLeaves=15, validationIndicatorCol="isVal", earlyStoppingRound=100, metric="auc",
+                                 samplingMode="fixed", dataTransferMode=mode, useQuantizedGrad=True, stochasticRounding=False)
+        est.fit(df)
+        hist[mode] = [h[1]["auc"] for h in est.performance_measures["evalHistory"]]
+    assert hist["streaming"] == hist["bulk"] and len(hist["bulk"]) == 5
+
