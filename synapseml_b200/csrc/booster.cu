@@ -115,7 +115,12 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   d_hist_work_.Alloc(hist_elems * kMaxBatch * 2);      // two parities (only the first is used without the peer exchange)
   work_stride_ = static_cast<long long>(hist_elems) * kMaxBatch;
   memset(&peers_, 0, sizeof(peers_));
-  if (net_->active() && net_->world() <= kMaxPeers && (getenv("LGB_B200_PEER_EXCHANGE") == nullptr || atoi(getenv("LGB_B200_PEER_EXCHANGE")) != 0)) {
+  // Every rank reads every rank's bins in this exchange (world x the payload per rank): right for narrow data, where a round is
+  // latency-bound (C2: 8 x 57 KB per rank), wrong for wide data (C5: 8 x 4 MB per rank x 8 ranks = 256 MB per round), which
+  // stays on NCCL's bandwidth-optimal all-reduce until the feature-sliced exchange exists.
+  const double exchange_bytes = static_cast<double>(lp_.quantized ? hist_elems / 2 : hist_elems) * sizeof(long long) * kMaxBatch * net_->world();
+  if (net_->active() && net_->world() <= kMaxPeers && exchange_bytes <= 16.0 * 1024 * 1024 &&
+      (getenv("LGB_B200_PEER_EXCHANGE") == nullptr || atoi(getenv("LGB_B200_PEER_EXCHANGE")) != 0)) {
     // histogram exchange over peer memory (batch_tree.cuh: PeerTable); falls back to NCCL all-reduce if the mapping fails
     d_peer_flags_.AllocZero(64);
     if (net_->ExchangePeerPointers(d_hist_work_.p, &peer_work_) && net_->ExchangePeerPointers(d_peer_flags_.p, &peer_flags_)) {
