@@ -773,29 +773,11 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
 // instead of going through the leaves' index ranges, and — for the row-wise objectives — computes the next iteration's
 // gradients and their max |g|, max |h| in the same pass (OBJ = 1 binary, 2 L2, 0 scores only).
 // The decisions are the partition kernel's: bin == nan_bin ? default_left : bin <= threshold.
-// A thread keeps its row's record in registers (WPR = 8 or 16 words; the bin is picked with selects, shared memory only
-// serves the 8-byte node table: one LDS per level); WPR = 0 reads the bins of wider records in place.
+// A thread keeps its row's record (WPR = 8 or 16 words) in a private, bank-staggered slice of shared memory, so a level costs two
+// shared loads — the 8-byte node and the bin byte — and a handful of ALU instructions (picking the byte out of registers with
+// selects was 25 % slower: the kernel is issue-bound); WPR = 0 reads the bins of wider records in place.
 constexpr int kApplyThreads = 256;
 constexpr int kApplyMaxFeatures = 1 << 14;      // node word: feature (14 bits) | nan bin (9) | threshold (8) | default_left (1)
-
-template <int WPR>
-__device__ __forceinline__ unsigned int PickBin(const unsigned int (&r)[WPR == 0 ? 1 : WPR], int f) {
-  const int w = f >> 2;
-  unsigned int v;
-  if (WPR == 8) {
-    const unsigned int t0 = (w & 1) ? r[1] : r[0], t1 = (w & 1) ? r[3] : r[2], t2 = (w & 1) ? r[5] : r[4], t3 = (w & 1) ? r[7] : r[6];
-    const unsigned int u0 = (w & 2) ? t1 : t0, u1 = (w & 2) ? t3 : t2;
-    v = (w & 4) ? u1 : u0;
-  } else {
-    unsigned int t[8];
-    #pragma unroll
-    for (int i = 0; i < 8; ++i) t[i] = (w & 1) ? r[(2 * i + 1) % (WPR == 0 ? 1 : WPR)] : r[(2 * i) % (WPR == 0 ? 1 : WPR)];
-    const unsigned int u0 = (w & 2) ? t[1] : t[0], u1 = (w & 2) ? t[3] : t[2], u2 = (w & 2) ? t[5] : t[4], u3 = (w & 2) ? t[7] : t[6];
-    const unsigned int x0 = (w & 4) ? u1 : u0, x1 = (w & 4) ? u3 : u2;
-    v = (w & 8) ? x1 : x0;
-  }
-  return (v >> ((f & 3) * 8)) & 0xffu;
-}
 
 template <int OBJ, int WPR>
 __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* __restrict__ rm, unsigned rm_stride,
@@ -825,16 +807,19 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
     }
   }
   __syncthreads();
+  // stride WPR + 1 words: for a given word (or byte) offset the 32 lanes of a warp fall into 32 different banks
+  __shared__ unsigned int s_rec[kApplyThreads * ((WPR == 0 ? 0 : WPR) + 1)];
+  unsigned int* my_rec = s_rec + threadIdx.x * (WPR + 1);
+  const unsigned char* my_bytes = reinterpret_cast<const unsigned char*>(my_rec);
   float mg = 0.0f, mh = 0.0f;
   for (long long row = static_cast<long long>(blockIdx.x) * kApplyThreads + threadIdx.x; row < n;
        row += static_cast<long long>(gridDim.x) * kApplyThreads) {
     const uint8_t* rec = rm + static_cast<size_t>(row) * rm_stride;
-    unsigned int r[WPR == 0 ? 1 : WPR];
-    if (WPR != 0) {
+    if (WPR != 0) {      // the thread's record goes into its private, bank-staggered slice of shared memory: a byte-indexable register file
       #pragma unroll
       for (int c = 0; c < WPR / 4; ++c) {
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(rec) + c);
-        r[4 * c] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+        my_rec[4 * c] = v.x; my_rec[4 * c + 1] = v.y; my_rec[4 * c + 2] = v.z; my_rec[4 * c + 3] = v.w;
       }
     }
     const double sc0 = score[row];
@@ -843,7 +828,7 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const uint2 nd = s_node[node];
       const int f = nd.x & 0x3fffu;
       const unsigned nan_bin = (nd.x >> 14) & 0x1ffu, thr = (nd.x >> 23) & 0xffu;
-      const unsigned bin = WPR != 0 ? PickBin<WPR>(r, f) : static_cast<unsigned>(__ldg(rec + f));
+      const unsigned bin = WPR != 0 ? static_cast<unsigned>(my_bytes[f]) : static_cast<unsigned>(__ldg(rec + f));
       const bool left = (bin == nan_bin) ? ((nd.x >> 31) != 0) : (bin <= thr);
       node = left ? static_cast<int>(static_cast<short>(nd.y & 0xffffu)) : static_cast<int>(static_cast<short>(nd.y >> 16));
     } while (node >= 0);
