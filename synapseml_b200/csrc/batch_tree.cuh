@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
 }
 
 // ------------------------------------------------------------------------------------------------ K7 (batched, one pass)
-// All leaves of the batch are cut into tiles of kPartTileRows rows; the CTAs walk the concatenated tile list, so the work is
+// All leaves of the batch are cut into tiles of kPartTileRows (1024) rows; the CTAs walk the concatenated tile list, so the work is
 // balanced whatever the leaf sizes are.  A tile reads its index entries once, looks up the split feature's bin of each row
 // (column-major copy), reserves room for its lefts and rights with ONE 64-bit atomic on the leaf's cursor (left count in the
 // high word, right count in the low word) and writes the entries to the other index buffer: lefts grow from the front of
@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
 // Every sum taken over a leaf's rows is an exact integer sum (quantized or fixed-point gradients), so the order of rows
 // inside a leaf does not change any result.  Nothing is "published" at the end: the consumers of the round (histogram, split
 // search) derive the children's row ranges from the final cursor value (MakeGeom).
-constexpr int kPartTileWords = 64;                        // 8 words per warp, 8 warps
+constexpr int kPartTileWords = 32;                        // 4 words per warp, 8 warps (measured: 2 -> 1.24, 4 -> 1.19, 8 -> 1.21, 16 -> 1.40 ms per iteration)
 constexpr int kPartTileRows = kPartTileWords * 32;
 
 // Tile list of the round (one thread): tiles[k] = first tile of batch item k, tiles[kMaxBatch] = total.
@@ -430,7 +430,7 @@ __device__ __forceinline__ void PartTileList(const BatchCtrl* ctrl, int bn, int*
 
 // Tiles vb, vb + nvb, ... by one 256-thread sub-block (named barriers: several sub-blocks can share a CTA).
 // A tile is a chain of three dependent memory round trips (entries -> bins -> cursor atomic) before its stores; what hides
-// them is the number of tiles in flight per SM (8192 rows), not anything inside one sub-block.
+// them is the number of tiles in flight per SM, not anything inside one sub-block.
 template <int ES>
 __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, long long n_pad, const int* idx0r, const int* idx1r,
                                                int* idx0w, int* idx1w, const uint16_t* __restrict__ gh16,
@@ -520,7 +520,7 @@ __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, l
 }
 
 template <int ES>
-__global__ void __launch_bounds__(kPartThreads, 4) k_bt_partition(const uint8_t* __restrict__ cm, long long n_pad,
+__global__ void __launch_bounds__(kPartThreads, 6) k_bt_partition(const uint8_t* __restrict__ cm, long long n_pad,
                                                                const int* __restrict__ idx0r, const int* __restrict__ idx1r,
                                                                int* __restrict__ idx0w, int* __restrict__ idx1w,
                                                                const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix,

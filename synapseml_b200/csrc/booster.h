@@ -213,7 +213,7 @@ class Booster {
   long long work_stride_ = 0;
   bool use_persistent_ = false;
   size_t persist_smem_ = 0;
-  int part_blocks_ = 592;                   // 4 x 148 SMs (k_bt_partition is built for 4 CTAs per SM)
+  int part_blocks_ = 888;                   // 6 x 148 SMs (k_bt_partition is built for 6 CTAs per SM)
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
   size_t hist_events_used_ = 0;
