@@ -11,7 +11,7 @@ namespace lgb {
 
 constexpr int kBins = 256;
 constexpr int kHistThreads = 1024;
-constexpr int kHistMinRowsPerCta = 2048;
+constexpr int kHistMinRowsPerCta = 256;      // measured on C2, 500 iterations: 8192 -> 1.230, 2048 -> 1.191, 512 -> 1.179, 256 -> 1.176 ms per iteration
 
 // Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization attribute may start
 // while its predecessor in the stream is still draining.  PdlLaunchDependents() lets the successor's CTAs become resident;
