@@ -770,7 +770,7 @@ void Dataset::SetFeatureNames(const char** names, int n) {
   feature_names.assign(names, names + n);
 }
 
-constexpr size_t kStageBytes = size_t(8) << 20;
+constexpr size_t kStageBytes = size_t(4) << 20;
 
 // Page-locked staging buffers are expensive to create (tens of milliseconds per 64 MB), so they are kept for the life of the
 // process and handed from one dataset to the next (a fit creates a dataset per executor; repeated fits reuse the buffers).
