@@ -83,6 +83,11 @@ int LGBM_DatasetMarkFinished(DatasetHandle dataset);
 /* dataset/DatasetAggregator.scala:413-421 (bulk mode): bin a whole row-major matrix; reference may be NULL */
 int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                               const char* parameters, const DatasetHandle reference, DatasetHandle* out);
+/* Bulk mode with sparse rows (LGBM/dataset/DatasetAggregator.scala: SparseAggregatedColumns.generateDataset): CSR in, same flow as
+ * CreateFromMat (bin mappers from `reference` or from the first bin_construct_sample_cnt rows). */
+int LGBM_DatasetCreateFromCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data, int data_type,
+                              int64_t nindptr, int64_t nelem, int64_t num_col, const char* parameters, const DatasetHandle reference,
+                              DatasetHandle* out);
 
 /* dataset/LightGBMDataset.scala:115,149,163 / :29 — field_name in {label, weight, init_score, group} */
 int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element, int type);

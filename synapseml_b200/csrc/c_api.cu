@@ -167,6 +167,52 @@ int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int
   API_END();
 }
 
+// Bulk mode, sparse rows (DatasetAggregator.scala: SparseAggregatedColumns.generateDataset).  Same flow as CreateFromMat: bin
+// mappers from `reference` or from the first bin_construct_sample_cnt rows, then all rows through the CSR push.
+int LGBM_DatasetCreateFromCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data, int data_type,
+                              int64_t nindptr, int64_t nelem, int64_t num_col, const char* parameters, const DatasetHandle reference,
+                              DatasetHandle* out) {
+  API_BEGIN();
+  LGB_CHECK(indptr_type == C_API_DTYPE_INT32 || indptr_type == C_API_DTYPE_INT64, "LGBM_DatasetCreateFromCSR: indptr must be int32 or int64");
+  LGB_CHECK(data_type == C_API_DTYPE_FLOAT64 || data_type == C_API_DTYPE_FLOAT32, "LGBM_DatasetCreateFromCSR: data must be float32 or float64");
+  const int64_t nrow = nindptr - 1;
+  const int ncol = static_cast<int>(num_col);
+  auto ptr_at = [&](int64_t i) -> int64_t {
+    return indptr_type == C_API_DTYPE_INT64 ? static_cast<const int64_t*>(indptr)[i] : static_cast<int64_t>(static_cast<const int32_t*>(indptr)[i]);
+  };
+  auto val_at = [&](int64_t j) -> double {
+    return data_type == C_API_DTYPE_FLOAT64 ? static_cast<const double*>(data)[j] : static_cast<double>(static_cast<const float*>(data)[j]);
+  };
+  std::unique_ptr<Dataset> ds;
+  if (reference != nullptr) {
+    ds.reset(static_cast<const Dataset*>(reference)->CreateByReference(nrow));
+  } else {
+    Config c;
+    c.Set(parameters ? parameters : "");
+    const int ns = static_cast<int>(std::min<int64_t>(nrow, c.bin_construct_sample_cnt));
+    std::vector<std::vector<double>> cols(ncol);
+    std::vector<std::vector<int>> idxs(ncol);
+    for (int i = 0; i < ns; ++i)
+      for (int64_t j = ptr_at(i); j < ptr_at(i + 1); ++j) {
+        const int col = indices[j];
+        LGB_CHECK(col >= 0 && col < ncol, "LGBM_DatasetCreateFromCSR: column index %d is outside [0, %d)", col, ncol);
+        const double v = val_at(j);
+        if (v != 0.0) { cols[col].push_back(v); idxs[col].push_back(i); }
+      }
+    std::vector<double*> dp(ncol);
+    std::vector<int*> ip(ncol);
+    std::vector<int> cnt(ncol);
+    for (int j = 0; j < ncol; ++j) { dp[j] = cols[j].data(); ip[j] = idxs[j].data(); cnt[j] = static_cast<int>(cols[j].size()); }
+    ds.reset(Dataset::CreateFromSampledColumn(dp.data(), ip.data(), ncol, cnt.data(), ns, static_cast<int>(nrow), nrow, parameters));
+  }
+  ds->wait_for_manual_finish = true;     // labels arrive through LGBM_DatasetSetField afterwards
+  ds->InitStreaming(false, false, false, 1, 1);
+  ds->PushRowsByCSR(indptr, indptr_type == C_API_DTYPE_INT64 ? 3 : 2, indices, data, data_type, nindptr, nelem, 0, nullptr, nullptr, nullptr,
+                    nullptr, 0);
+  *out = ds.release();
+  API_END();
+}
+
 int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element, int type) {
   API_BEGIN();
   auto ds = static_cast<Dataset*>(handle);

@@ -193,10 +193,21 @@ class BulkPartitionTask(BasePartitionTask):
         label / weight / init_score / group through LGBM_DatasetSetField (LightGBMDataset.scala:110-176)."""
         ctx = self.ctx
         lib = lightgbmlib()
-        X = np.ascontiguousarray(np.concatenate([p["features"] for p in partitions]), dtype=np.float64)
         handle = C.c_void_p()
-        validate(lib.LGBM_DatasetCreateFromMat(X.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(X.shape[0]), C.c_int32(X.shape[1]),
-                                               C.c_int(1), ctx["dataset_params"].encode(), None, C.byref(handle)), "Dataset create")
+        if any(hasattr(p["features"], "indptr") for p in partitions):
+            # SparseAggregatedColumns.generateDataset (DatasetAggregator.scala): one CSR block for the executor
+            import scipy.sparse as sp
+            M = sp.vstack([sp.csr_matrix(p["features"]) for p in partitions]).tocsr()
+            indptr = np.ascontiguousarray(M.indptr, dtype=np.int64)
+            indices = np.ascontiguousarray(M.indices, dtype=np.int32)
+            values = np.ascontiguousarray(M.data, dtype=np.float64)
+            validate(lib.LGBM_DatasetCreateFromCSR(indptr.ctypes.data_as(C.c_void_p), C.c_int(3), indices.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                   values.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int64(len(indptr)), C.c_int64(len(values)),
+                                                   C.c_int64(M.shape[1]), ctx["dataset_params"].encode(), None, C.byref(handle)), "Dataset create")
+        else:
+            X = np.ascontiguousarray(np.concatenate([p["features"] for p in partitions]), dtype=np.float64)
+            validate(lib.LGBM_DatasetCreateFromMat(X.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(X.shape[0]), C.c_int32(X.shape[1]),
+                                                   C.c_int(1), ctx["dataset_params"].encode(), None, C.byref(handle)), "Dataset create")
         ds = LightGBMDataset(handle)
         ds.add_float_field(np.concatenate([p["label"] for p in partitions]), "label")
         if any("weight" in p for p in partitions):

@@ -121,4 +121,6 @@ def test_sparse_partitions_give_the_dense_model(native):
         p["features"] = sp.csr_matrix(p["features"])
     sparse = LightGBMClassifier(**kw).fit(LocalDataFrame(parts)).getNativeModel()
     assert sparse == dense
+    bulk_sparse = LightGBMClassifier(dataTransferMode="bulk", **kw).fit(LocalDataFrame(parts)).getNativeModel()
+    assert bulk_sparse.split("parameters:")[0] == dense.split("parameters:")[0]
 
