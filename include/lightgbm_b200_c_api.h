@@ -186,6 +186,14 @@ int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_ty
 int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                               int predict_type, int start_iteration, int num_iteration, const char* parameter, int64_t* out_len,
                               double* out_result);
+/* sparse rows (LGBM/booster/LightGBMBooster.scala:520-538): expanded to dense on the host (absent = 0.0), then the same kernel */
+int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices, const void* data,
+                              int data_type, int64_t nindptr, int64_t nelem, int64_t num_col, int predict_type, int start_iteration,
+                              int num_iteration, const char* parameter, int64_t* out_len, double* out_result);
+int LGBM_BoosterPredictForCSRSingleRow(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices,
+                                       const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t num_col,
+                                       int predict_type, int start_iteration, int num_iteration, const char* parameter,
+                                       int64_t* out_len, double* out_result);
 int LGBM_BoosterPredictForMatSingleRow(BoosterHandle handle, const void* data, int data_type, int ncol, int is_row_major,
                                        int predict_type, int start_iteration, int num_iteration, const char* parameter,
                                        int64_t* out_len, double* out_result);

@@ -477,6 +477,40 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
                                                num_iteration, out_result, out_len);
   API_END();
 }
+// Sparse rows for scoring (LightGBMBooster.scala:520-538, predictForCSR): the rows are expanded to dense (absent = 0.0, a host-side
+// formatting step) and scored by the same GPU kernel as PredictForMat.
+int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices, const void* data,
+                              int data_type, int64_t nindptr, int64_t nelem, int64_t num_col, int predict_type, int start_iteration,
+                              int num_iteration, const char* /*parameter*/, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  LGB_CHECK(indptr_type == C_API_DTYPE_INT32 || indptr_type == C_API_DTYPE_INT64, "PredictForCSR: indptr must be int32 or int64");
+  LGB_CHECK(data_type == C_API_DTYPE_FLOAT64 || data_type == C_API_DTYPE_FLOAT32, "PredictForCSR: data must be float32 or float64");
+  auto b = static_cast<Booster*>(handle);
+  const int64_t nrow = nindptr - 1;
+  const int ncol = b->NumTotalFeatures();
+  LGB_CHECK(num_col <= ncol, "PredictForCSR: %lld columns, the model has %d features", (long long)num_col, ncol);
+  auto ptr_at = [&](int64_t i) -> int64_t {
+    return indptr_type == C_API_DTYPE_INT64 ? static_cast<const int64_t*>(indptr)[i] : static_cast<int64_t>(static_cast<const int32_t*>(indptr)[i]);
+  };
+  LGB_CHECK(nrow <= 0 || ptr_at(nrow) - ptr_at(0) <= nelem, "PredictForCSR: indptr does not match nelem");
+  std::vector<double> dense(static_cast<size_t>(std::max<int64_t>(nrow, 0)) * ncol, 0.0);
+  for (int64_t i = 0; i < nrow; ++i)
+    for (int64_t j = ptr_at(i); j < ptr_at(i + 1); ++j) {
+      const int c = indices[j];
+      LGB_CHECK(c >= 0 && c < ncol, "PredictForCSR: column index %d is outside [0, %d)", c, ncol);
+      dense[static_cast<size_t>(i) * ncol + c] =
+          data_type == C_API_DTYPE_FLOAT64 ? static_cast<const double*>(data)[j] : static_cast<double>(static_cast<const float*>(data)[j]);
+    }
+  b->PredictForMat(dense.data(), C_API_DTYPE_FLOAT64, nrow, ncol, true, predict_type, start_iteration, num_iteration, out_result, out_len);
+  API_END();
+}
+int LGBM_BoosterPredictForCSRSingleRow(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices,
+                                       const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t num_col,
+                                       int predict_type, int start_iteration, int num_iteration, const char* parameter,
+                                       int64_t* out_len, double* out_result) {
+  return LGBM_BoosterPredictForCSR(handle, indptr, indptr_type, indices, data, data_type, nindptr, nelem, num_col, predict_type,
+                                   start_iteration, num_iteration, parameter, out_len, out_result);
+}
 int LGBM_BoosterPredictForMatSingleRow(BoosterHandle handle, const void* data, int data_type, int ncol, int is_row_major,
                                        int predict_type, int start_iteration, int num_iteration, const char* /*parameter*/,
                                        int64_t* out_len, double* out_result) {

@@ -86,6 +86,19 @@ def test_normal_leaf_subrange_layouts_and_single_row(native, trained):
                                          o.ctypes.data_as(C.POINTER(C.c_double))) == -1
 
 
+def test_sparse_rows_score_like_dense_rows(native, trained):
+    import scipy.sparse as sp
+    X, nb = trained
+    Xz = np.nan_to_num(X[:3000])
+    M = sp.csr_matrix(Xz)
+    indptr, indices, vals = M.indptr.astype(np.int32), M.indices.astype(np.int32), M.data.astype(np.float64)
+    out, n = np.zeros(len(Xz)), C.c_int64()
+    validate(lightgbmlib().LGBM_BoosterPredictForCSR(nb.handle, indptr.ctypes.data_as(C.c_void_p), 2, indices.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                     vals.ctypes.data_as(C.c_void_p), 1, C.c_int64(len(indptr)), C.c_int64(len(vals)),
+                                                     C.c_int64(X.shape[1]), 1, 0, -1, b"", C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+    assert n.value == len(Xz) and np.array_equal(out, predict(nb.handle, Xz, 1))
+
+
 def test_booster_rebuilt_from_the_model_string_predicts_identically(native, trained):
     X, nb = trained
     text = nb.model()
