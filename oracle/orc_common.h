@@ -17,6 +17,7 @@
 #include <cstring>
 #include <limits>
 #include <map>
+#include <set>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -113,6 +114,39 @@ inline float HashUniform(uint32_t seed, uint32_t iter, uint32_t row, uint32_t wh
   return static_cast<float>(h >> 8) * (1.0f / 16777216.0f);
 }
 
+// include/LightGBM/utils/random.h (upstream): x = 214013 x + 2531011 (mod 2^32); 15-bit draws for NextShort / NextFloat,
+// 31-bit draws for NextInt.
+struct Random {
+  unsigned int x = 123456789u;
+  Random() {}
+  explicit Random(int seed) : x(static_cast<unsigned int>(seed)) {}
+  int RandInt16() { x = 214013u * x + 2531011u; return static_cast<int>((x >> 16) & 0x7FFF); }
+  int RandInt32() { x = 214013u * x + 2531011u; return static_cast<int>(x & 0x7FFFFFFF); }
+  int NextShort(int lo, int hi) { return RandInt16() % (hi - lo) + lo; }
+  int NextInt(int lo, int hi) { return RandInt32() % (hi - lo) + lo; }
+  float NextFloat() { return static_cast<float>(RandInt16()) / 32768.0f; }
+  // Random::Sample(N, K): K distinct values of [0, N), ascending
+  std::vector<int> Sample(int N, int K) {
+    std::vector<int> ret;
+    if (K > N || K <= 0) return ret;
+    if (K == N) { for (int i = 0; i < N; ++i) ret.push_back(i); return ret; }
+    if (K > 1 && K > (N / std::log2(static_cast<double>(K)))) {
+      for (int i = 0; i < N; ++i) {
+        const double prob = (K - static_cast<int>(ret.size())) / static_cast<double>(N - i);
+        if (NextFloat() < prob) ret.push_back(i);
+      }
+    } else {
+      std::set<int> chosen;
+      for (int r = N - K; r < N; ++r) {
+        const int v = NextInt(0, r);
+        if (!chosen.insert(v).second) chosen.insert(r);
+      }
+      for (int v : chosen) ret.push_back(v);
+    }
+    return ret;
+  }
+};
+
 struct Config {
   std::string objective = "regression";
   std::string boosting = "gbdt";
@@ -142,6 +176,11 @@ struct Config {
   bool stochastic_rounding = true;
   bool quant_train_renew_leaf = false;
   int seed = 0;
+  // column / row sampling (upstream config.h defaults); `seed` derives the specific seeds (Config::Set, upstream src/io/config.cpp)
+  double feature_fraction = 1.0;
+  int feature_fraction_seed = 2;
+  double bagging_fraction = 1.0;
+  int bagging_freq = 0, bagging_seed = 3;
   int num_machines = 1;
   int num_threads = 0;
   int verbosity = 1;
@@ -175,6 +214,9 @@ struct Config {
         {"unbalance", "is_unbalance"}, {"unbalanced_sets", "is_unbalance"},
         {"num_thread", "num_threads"}, {"nthread", "num_threads"}, {"nthreads", "num_threads"}, {"n_jobs", "num_threads"},
         {"random_seed", "seed"}, {"random_state", "seed"},
+        {"sub_feature", "feature_fraction"}, {"colsample_bytree", "feature_fraction"},
+        {"sub_row", "bagging_fraction"}, {"subsample", "bagging_fraction"}, {"bagging", "bagging_fraction"},
+        {"subsample_freq", "bagging_freq"}, {"bagging_fraction_seed", "bagging_seed"},
         {"num_machine", "num_machines"},
         {"verbose", "verbosity"},
         {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"},
@@ -246,6 +288,19 @@ struct Config {
     getb("stochastic_rounding", &stochastic_rounding);
     getb("quant_train_renew_leaf", &quant_train_renew_leaf);
     geti("seed", &seed);
+    if (has("seed")) {     // upstream: Random rand(seed); the specific seeds are NextShort(0, int16 max) draws in declaration order
+      Random r(seed);
+      const int int_max = 32767;
+      r.NextShort(0, int_max);                       // data_random_seed
+      bagging_seed = r.NextShort(0, int_max);
+      r.NextShort(0, int_max);                       // drop_seed
+      feature_fraction_seed = r.NextShort(0, int_max);
+    }
+    getd("feature_fraction", &feature_fraction);
+    geti("feature_fraction_seed", &feature_fraction_seed);
+    getd("bagging_fraction", &bagging_fraction);
+    geti("bagging_freq", &bagging_freq);
+    geti("bagging_seed", &bagging_seed);
     geti("num_machines", &num_machines);
     geti("num_threads", &num_threads);
     geti("verbosity", &verbosity);

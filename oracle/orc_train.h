@@ -245,6 +245,10 @@ struct Shard {
   std::vector<int8_t> qg, qh;             // quantized gradient / hessian
   std::vector<data_size_t> indices, tmp_left, tmp_right;
   std::vector<data_size_t> leaf_begin, leaf_count;
+  // bagging (upstream src/boosting/bagging.hpp): in-bag rows ascending in [0, bag_cnt), the others behind them
+  std::vector<data_size_t> bag_indices;
+  data_size_t bag_cnt = 0;
+  std::vector<Random> bag_rands;          // one stream per block of 1024 rows, seeded bagging_seed + block
 };
 
 class Booster {
@@ -276,6 +280,10 @@ class Booster {
   std::vector<std::vector<double>> hist_f;   // per leaf: F*B*2 doubles
   std::vector<std::vector<int64_t>> hist_i;  // per leaf: F*B*2 int64
   int64_t total_rows = 0;
+  // column / row sampling
+  Random feature_rand;
+  std::vector<char> tree_mask;             // this tree's column sample (all ones when feature_fraction == 1)
+  bool bagging = false;
 
   Booster(const std::vector<const Dataset*>& ds, const char* params) {
     cfg = ds[0]->config;     // dataset-time params (max_bin ...) first, booster string overrides
@@ -304,7 +312,43 @@ class Booster {
     sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf};
     if (cfg.boosting != "gbdt") throw std::runtime_error("oracle: only boosting=gbdt is restated");
     if (cfg.zero_as_missing) throw std::runtime_error("oracle: zero_as_missing is not restated");
+    feature_rand = Random(cfg.feature_fraction_seed);
+    tree_mask.assign(F, 1);
+    bagging = cfg.bagging_freq > 0 && cfg.bagging_fraction < 1.0;
+    for (auto& sh : shards) {
+      const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
+      sh.bag_cnt = n;
+      if (bagging) {       // ResetSampleConfig: every machine seeds its blocks alike (bagging is local to a machine)
+        sh.bag_indices.resize(n);
+        for (data_size_t b = 0; b < (n + 1023) / 1024; ++b) sh.bag_rands.emplace_back(cfg.bagging_seed + static_cast<int>(b));
+      }
+    }
     InitObjective();
+  }
+
+  // BaggingSampleStrategy::Bagging + BaggingHelper: at iterations that are multiples of bagging_freq every row draws once from
+  // the stream of its 1024-row block and is in the bag when the draw is below bagging_fraction.  (The subset copy upstream makes
+  // for small bags changes no tree; the discretizer then sees the bag only — this restatement always uses all rows for the scales.)
+  void Bagging() {
+    if (!bagging || iter % cfg.bagging_freq != 0) return;
+    for (auto& sh : shards) {
+      const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
+      data_size_t left = 0, right = n;
+      for (data_size_t i = 0; i < n; ++i) {
+        if (sh.bag_rands[i / 1024].NextFloat() < cfg.bagging_fraction) sh.bag_indices[left++] = i;
+        else sh.bag_indices[--right] = i;
+      }
+      sh.bag_cnt = left;
+    }
+  }
+
+  // ColSampler::ResetByTree
+  void SampleFeatures() {
+    if (!(cfg.feature_fraction < 1.0)) return;
+    const int min_cnt = std::min(2, F);
+    const int cnt = std::max(static_cast<int>(F * cfg.feature_fraction + 0.5), min_cnt);
+    tree_mask.assign(F, 0);
+    for (int f : feature_rand.Sample(F, cnt)) tree_mask[f] = 1;
   }
 
   // ---------------------------------------------------------------- objectives
@@ -614,23 +658,25 @@ class Booster {
     leaves.assign(NL, Leaf());
     for (auto& L : leaves) L.splittable.assign(F, 1);
     if (q) hist_i.resize(NL); else hist_f.resize(NL);
+    SampleFeatures();
+    Leaf& root = leaves[0];
     for (auto& sh : shards) {
-      std::iota(sh.indices.begin(), sh.indices.end(), 0);
+      if (bagging) std::copy(sh.bag_indices.begin(), sh.bag_indices.begin() + sh.bag_cnt, sh.indices.begin());   // SetBaggingData
+      else std::iota(sh.indices.begin(), sh.indices.end(), 0);
       std::fill(sh.leaf_begin.begin(), sh.leaf_begin.end(), 0);
       std::fill(sh.leaf_count.begin(), sh.leaf_count.end(), 0);
-      sh.leaf_count[0] = static_cast<data_size_t>(sh.ds->num_data);
+      sh.leaf_count[0] = sh.bag_cnt;
+      root.count += sh.bag_cnt;
     }
-    // root sums
-    Leaf& root = leaves[0];
-    root.count = static_cast<data_size_t>(total_rows);
+    // root sums (over the rows in the bag)
     if (q) {
-      for (auto& sh : shards) for (size_t i = 0; i < sh.qg.size(); ++i) { root.int_g += sh.qg[i]; root.int_h += sh.qh[i]; }
+      for (auto& sh : shards) for (data_size_t i = 0; i < sh.bag_cnt; ++i) { root.int_g += sh.qg[sh.indices[i]]; root.int_h += sh.qh[sh.indices[i]]; }
       root.sum_g = static_cast<double>(root.int_g) * grad_scale;
       root.sum_h = static_cast<double>(root.int_h) * hess_scale;
     } else {
       for (auto& sh : shards) {
         double sg = 0.0, shh = 0.0;
-        for (size_t i = 0; i < sh.grad.size(); ++i) { sg += sh.grad[i]; shh += sh.hess[i]; }
+        for (data_size_t i = 0; i < sh.bag_cnt; ++i) { sg += sh.grad[sh.indices[i]]; shh += sh.hess[sh.indices[i]]; }
         root.sum_g += sg; root.sum_h += shh;
       }
     }
@@ -654,7 +700,7 @@ class Booster {
         }
         if (go) {
           if (right_leaf < 0) {
-            std::vector<char> used(F, 1);
+            std::vector<char> used(tree_mask);
             ConstructHistogram(0, used);
             FindBestForLeaf(0, used);
           } else {
@@ -662,7 +708,7 @@ class Booster {
             int larger = nl < nr ? right_leaf : left_leaf;
             // the parent's histogram lives in slot left_leaf; features unsplittable at the parent stay so in both children
             std::vector<char> used(F, 1);
-            for (int f = 0; f < F; ++f) used[f] = leaves[left_leaf].splittable[f];
+            for (int f = 0; f < F; ++f) used[f] = leaves[left_leaf].splittable[f] && tree_mask[f];
             if (q) { if (larger != left_leaf) hist_i[larger].swap(hist_i[left_leaf]); }
             else { if (larger != left_leaf) hist_f[larger].swap(hist_f[left_leaf]); }
             ConstructHistogram(smaller, used);
@@ -739,6 +785,7 @@ class Booster {
       }
     }
     GetGradients();
+    Bagging();
     bool should_continue = false;
     std::unique_ptr<Tree> tree(new Tree(2));
     if (need_train && F > 0) tree = TrainTree();
@@ -750,6 +797,11 @@ class Booster {
           const double out = tree->leaf_value[l];
           const data_size_t b = sh.leaf_begin[l], n = sh.leaf_count[l];
           for (data_size_t i = 0; i < n; ++i) sh.score[sh.indices[b + i]] += out;
+        }
+        // out-of-bag rows: ScoreUpdater::AddScore(tree, indices, cnt) walks the tree over the row's bins
+        for (data_size_t i = sh.bag_cnt; bagging && i < static_cast<data_size_t>(sh.ds->num_data); ++i) {
+          const data_size_t r = sh.bag_indices[i];
+          sh.score[r] += tree->leaf_value[LeafByBins(*tree, sh.ds, r)];
         }
       }
       if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
@@ -765,6 +817,24 @@ class Booster {
     }
     ++iter;
     return false;
+  }
+
+  // Tree::AddPredictionToScore's inner decision over bins (numerical): NaN bin follows default_left, else bin <= threshold
+  static int LeafByBins(const Tree& t, const Dataset* d, data_size_t row) {
+    if (t.num_leaves <= 1) return 0;
+    int node = 0;
+    while (node >= 0) {
+      const int f = t.split_feature_inner[node];
+      const BinMapper& m = d->inner_mapper(f);
+      const uint32_t bin = d->bin_at(f, row);
+      const int mt = (t.decision_type[node] >> 2) & 3;
+      const bool dl = (t.decision_type[node] & 2) != 0;
+      bool left;
+      if (mt == MISSING_NAN && bin == static_cast<uint32_t>(m.num_bin - 1)) left = dl;
+      else left = bin <= t.threshold_in_bin[node];
+      node = left ? t.left_child[node] : t.right_child[node];
+    }
+    return ~node;
   }
 
   std::string ObjectiveString() const {

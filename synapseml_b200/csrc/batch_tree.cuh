@@ -89,6 +89,9 @@ struct BatchCtrl {
   // optional timeline for experiments (LGB_B200_TRACE=1): (event id, %globaltimer ns) pairs written by CTA 0 of every kernel
   long long* trace;
   int trace_n, trace_cap;
+  // bagging: bit r = row r is in this iteration's bag (nullptr: every row is).  Rows outside the bag carry zero gradients into
+  // the root histogram and are dropped by the root's partition, so below the root only rows of the bag exist.
+  const unsigned int* bag_bits;
 };
 
 __device__ __forceinline__ void Trace(BatchCtrl* ctrl, int id) {
@@ -102,6 +105,7 @@ __device__ __forceinline__ void Trace(BatchCtrl* ctrl, int id) {
 
 struct ChildGeom {
   int nl, nr;              // rows that went left / right on this GPU
+  int rbegin;              // first position of the right child's rows (the rights are placed from the parent's back)
   int lc, rc;              // counts the split search uses: nl / nr (serial learner) or the estimates (data-parallel)
   int buf;                 // index buffer the children live in
   bool left_smaller, find;
@@ -109,7 +113,8 @@ struct ChildGeom {
 __device__ __forceinline__ ChildGeom MakeGeom(const BatchItem& it, unsigned long long cursor, const LearnerParams& P) {
   ChildGeom g;
   g.nl = static_cast<int>(cursor >> 32);
-  g.nr = it.src_count - g.nl;
+  g.nr = static_cast<int>(cursor & 0xffffffffu);      // = src_count - nl except below a bagged root, which drops rows
+  g.rbegin = it.src_begin + it.src_count - g.nr;
   g.lc = P.dp ? it.est_left : g.nl;
   g.rc = P.dp ? it.est_right : g.nr;
   g.buf = it.src_buf < 0 ? 0 : 1 - it.src_buf;
@@ -177,7 +182,7 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
         const BatchItem& it = ctrl->batch[k];
         const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
         if (g.find) {
-          sh->begin[k] = g.left_smaller ? it.src_begin : it.src_begin + g.nl;
+          sh->begin[k] = g.left_smaller ? it.src_begin : g.rbegin;
           sh->buf[k] = g.buf;
           cnt = g.left_smaller ? g.nl : g.nr;
           ++active;
@@ -284,7 +289,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
     parent = it.node;
     parent_slot = it.parent_slot;
     find = g.find;
-    me.begin = is_left ? it.src_begin : it.src_begin + g.nl;
+    me.begin = is_left ? it.src_begin : g.rbegin;
     me.count = is_left ? g.nl : g.nr;
     me.buf = g.buf;
     me.global_count = is_left ? g.lc : g.rc;
@@ -339,11 +344,15 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
   unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
   long long tg = me.int_g, th = me.int_h;
-  if (!used) {
+  // column sample of this tree (feature_fraction): a feature outside it has no split.  At the root it still runs the search,
+  // because the leaf totals come out of it, and its result is discarded.
+  const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
+  if (!used || (!sampled && !root)) {
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
     BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
                          fb + f, spl, &tg, &th, sub);
+    if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
   }
   __threadfence();
   SubSync(sub);
@@ -453,6 +462,7 @@ __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, l
     const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left;
     const uint8_t* col = cm + static_cast<size_t>(it.feature) * n_pad;
     const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
+    const unsigned int* bag = buf < 0 ? ctrl->bag_bits : nullptr;
     int* dst = (buf < 0 ? 0 : 1 - buf) == 0 ? idx0w : idx1w;
     const int p_base = (tile - s_tiles[k]) * kPartTileRows + warp * (WPW * 32) + lane;
     int4 ent[WPW];
@@ -464,7 +474,8 @@ __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, l
         if (idx) {
           if (ES == 2) { const int2 e = reinterpret_cast<const int2*>(idx)[begin + p]; ent[u].x = e.x; ent[u].y = e.y; }
           else ent[u] = reinterpret_cast<const int4*>(idx)[begin + p];
-        } else {             // the root: rows are 0..n-1, gradients come from the per-row arrays
+        } else if (bag == nullptr || ((bag[(begin + p) >> 5] >> ((begin + p) & 31)) & 1u)) {
+          // the root: rows are 0..n-1 (those in the bag), gradients come from the per-row arrays
           const int row = begin + p;
           ent[u].x = row;
           if (ES == 2) {

@@ -59,6 +59,20 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   LGB_CHECK(train->num_features() <= kApplyMaxFeatures, "more than %d used features are not supported", kApplyMaxFeatures);
   LGB_CHECK(!cfg_.zero_as_missing, "zero_as_missing=true is not supported by this library yet");
   LGB_CHECK(cfg_.num_grad_quant_bins >= 2 && cfg_.num_grad_quant_bins <= 64, "num_grad_quant_bins=%d is outside [2, 64]", cfg_.num_grad_quant_bins);
+  LGB_CHECK(cfg_.feature_fraction > 0.0 && cfg_.feature_fraction <= 1.0, "feature_fraction=%g is outside (0, 1]", cfg_.feature_fraction);
+  // parameters that would change the model and are not implemented are refused rather than ignored
+  LGB_CHECK(cfg_.feature_fraction_bynode == 1.0, "feature_fraction_bynode < 1 is not supported by this library yet");
+  LGB_CHECK(cfg_.bagging_fraction > 0.0 && cfg_.bagging_fraction <= 1.0, "bagging_fraction=%g is outside (0, 1]", cfg_.bagging_fraction);
+  LGB_CHECK(!(cfg_.bagging_freq > 0 && (cfg_.pos_bagging_fraction < 1.0 || cfg_.neg_bagging_fraction < 1.0)),
+            "balanced bagging (pos_bagging_fraction / neg_bagging_fraction < 1) is not supported by this library yet");
+  for (const char* key : {"monotone_constraints", "max_bin_by_feature", "interaction_constraints", "forcedsplits_filename",
+                          "cegb_penalty_split", "linear_tree", "extra_trees", "path_smooth", "feature_contri"}) {
+    auto it = cfg_.raw.find(key);
+    if (it == cfg_.raw.end()) continue;
+    const std::string& v = it->second;
+    const bool off = v.empty() || v == "0" || v == "0.0" || v == "false" || v == "False";
+    LGB_CHECK(off, "%s=%s is not supported by this library yet", key, v.c_str());
+  }
   device_ = train->device;
   LGB_CUDA(cudaSetDevice(device_));
   LGB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
@@ -91,6 +105,12 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   lp_.num_grad_quant_bins = cfg_.num_grad_quant_bins; lp_.stochastic_rounding = cfg_.stochastic_rounding;
   lp_.const_hessian = (obj_ == kL2 && !has_weights_);
   lp_.seed = static_cast<unsigned int>(cfg_.seed);
+  lp_.feature_mask = nullptr;
+  if (cfg_.feature_fraction < 1.0 && F_ > 0) {
+    d_feature_mask_.Alloc(F_);
+    lp_.feature_mask = d_feature_mask_.p;
+    feature_rand_ = HostRandom(cfg_.feature_fraction_seed);
+  }
 
   const int L = cfg_.num_leaves;
   d_score_.AllocZero(n_);
@@ -153,6 +173,18 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     hc.trace = nullptr; hc.trace_cap = trace_cap_;
     LGB_CUDA(cudaMemcpy(d_ctrl_, &hc, sizeof(hc), cudaMemcpyHostToDevice));
     if (const char* from = getenv("LGB_B200_TRACE_FROM")) trace_from_ = atoi(from);
+  }
+  bagging_ = cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0;
+  if (bagging_) {      // ResetSampleConfig: one LCG stream per block of 1024 local rows, seeded bagging_seed + block
+    const int nblk = static_cast<int>((n_ + 1023) / 1024);
+    std::vector<unsigned int> seeds(nblk);
+    for (int b = 0; b < nblk; ++b) seeds[b] = static_cast<unsigned int>(cfg_.bagging_seed + b);
+    d_bag_rand_.Alloc(nblk);
+    LGB_CUDA(cudaMemcpy(d_bag_rand_.p, seeds.data(), sizeof(unsigned int) * nblk, cudaMemcpyHostToDevice));
+    d_bag_bits_.AllocZero(static_cast<size_t>(nblk) * 32);
+    d_bag_count_.AllocZero(1);
+    const unsigned int* bits = d_bag_bits_.p;
+    LGB_CUDA(cudaMemcpy(&d_ctrl_->bag_bits, &bits, sizeof(bits), cudaMemcpyHostToDevice));
   }
   d_avail_.AllocZero(L);
   d_feat_best_.Alloc(static_cast<size_t>(2) * kMaxBatch * std::max(F_, 1));
@@ -393,7 +425,8 @@ void Booster::PrepareGradients(bool absmax_ready) {
   if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
   k_scales<<<1, 1, 0, stream_>>>(d_ctrl_, lp_);
   k_quantize<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
-                                        static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p);
+                                        static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p,
+                                        bagging_ ? d_bag_bits_.p : nullptr);
   LGB_CUDA(cudaGetLastError());
   launches_ += 3;
 }
@@ -539,6 +572,36 @@ void Booster::EnqueueRounds(int rounds) {
   }
 }
 
+// ColSampler::ResetByTree (upstream src/treelearner/col_sampler.hpp): every tree draws max(round(F * feature_fraction), min(2, F))
+// of the used features from one LCG stream; every rank draws the same (same seed, same F).  The split search treats the others
+// as if they had no valid threshold.
+// BaggingSampleStrategy::Bagging: a new bag at every iteration that is a multiple of bagging_freq (each rank over its own rows).
+// The root's row count is the number of rows in the bags of all ranks.
+void Booster::Bagging() {
+  if (!bagging_ || iter_ % cfg_.bagging_freq != 0) return;
+  const int n = static_cast<int>(n_);
+  LGB_CUDA(cudaMemsetAsync(d_bag_count_.p, 0, sizeof(int), stream_));
+  k_bag_sample<<<CeilDiv(CeilDiv(n, 1024), 64), 64, 0, stream_>>>(d_bag_rand_.p, n, cfg_.bagging_fraction, d_bag_bits_.p, d_bag_count_.p);
+  LGB_CUDA(cudaGetLastError());
+  ++launches_;
+  int local = 0;
+  LGB_CUDA(cudaMemcpyAsync(&local, d_bag_count_.p, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+  LGB_CUDA(cudaStreamSynchronize(stream_));
+  std::vector<long long> all;
+  net_->HostAllGatherInt64(local, &all);
+  bag_cnt_global_ = 0;
+  for (long long c : all) bag_cnt_global_ += c;
+}
+
+void Booster::SampleFeaturesForTree() {
+  const int min_cnt = std::min(2, F_);
+  const int cnt = std::max(static_cast<int>(F_ * cfg_.feature_fraction + 0.5), min_cnt);
+  std::vector<unsigned char> mask(F_, 0);
+  for (int f : feature_rand_.Sample(F_, cnt)) mask[f] = 1;
+  // pageable source: the runtime stages it before the call returns, so the vector may go out of scope
+  LGB_CUDA(cudaMemcpyAsync(d_feature_mask_.p, mask.data(), F_, cudaMemcpyHostToDevice, stream_));
+}
+
 void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
@@ -548,7 +611,9 @@ void Booster::TrainTree(HostTree* out) {
     LGB_CUDA(cudaMemcpyAsync(&d_ctrl_->trace, &p, sizeof(p), cudaMemcpyHostToDevice, stream_));
     LGB_CUDA(cudaStreamSynchronize(stream_));
   }
-  k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n, static_cast<int>(n_global_));
+  if (lp_.feature_mask != nullptr) SampleFeaturesForTree();
+  k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n,
+                                                  static_cast<int>(bagging_ ? bag_cnt_global_ : n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
   if (use_persistent_ && !time_hist_ && !prof_) {
@@ -714,6 +779,7 @@ bool Booster::UpdateOneIter() {
     if (fused) grad_cur_ ^= 1;
     else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
     grad_ready_ = false;
+    Bagging();
     ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
     TrainTree(&tree);
     if (tree.num_leaves <= 1) grad_ready_ = false;      // no tree, so the apply pass did nothing

@@ -73,6 +73,7 @@ struct LearnerParams {
   int min_data_in_leaf, max_depth, num_leaves, num_features;
   int quantized, dp, num_grad_quant_bins, stochastic_rounding, const_hessian;
   unsigned int seed;
+  const unsigned char* feature_mask;      // [F] 1 = this tree may split on the feature (feature_fraction < 1), nullptr = all
 };
 
 class Booster {
@@ -185,6 +186,15 @@ class Booster {
   int max_nodes_ = 0, spec_budget_ = 0, max_batch_ = 4, last_rounds_ = 0;
   DevBuf<SplitDev> d_feat_best_;     // [2][F]
   DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
+  DevBuf<unsigned char> d_feature_mask_; // [F] this tree's column sample (feature_fraction < 1 only)
+  HostRandom feature_rand_{2};           // ColSampler's stream, seeded with feature_fraction_seed
+  void SampleFeaturesForTree();
+  // bagging (bagging_freq > 0, bagging_fraction < 1): the bag as a bit per row, re-drawn every bagging_freq iterations
+  bool bagging_ = false;
+  DevBuf<unsigned int> d_bag_bits_, d_bag_rand_;
+  DevBuf<int> d_bag_count_;
+  long long bag_cnt_global_ = 0;
+  void Bagging();
   DevBuf<unsigned char> d_tree_blob_;
   TreeArraysDev tree_dev_{};
   size_t tree_blob_bytes_ = 0;

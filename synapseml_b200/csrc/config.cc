@@ -2,10 +2,34 @@
 
 #include <algorithm>
 #include <cctype>
+#include <cmath>
+#include <set>
 #include <sstream>
 #include <stdexcept>
 
 namespace lgb {
+
+std::vector<int> HostRandom::Sample(int N, int K) {
+  std::vector<int> ret;
+  if (K > N || K <= 0) return ret;
+  ret.reserve(K);
+  if (K == N) {
+    for (int i = 0; i < N; ++i) ret.push_back(i);
+  } else if (K > 1 && K > (N / std::log2(static_cast<double>(K)))) {
+    for (int i = 0; i < N; ++i) {
+      const double prob = (K - static_cast<int>(ret.size())) / static_cast<double>(N - i);
+      if (NextFloat() < prob) ret.push_back(i);
+    }
+  } else {
+    std::set<int> chosen;
+    for (int r = N - K; r < N; ++r) {
+      const int v = NextInt(0, r);
+      if (!chosen.insert(v).second) chosen.insert(r);
+    }
+    ret.assign(chosen.begin(), chosen.end());
+  }
+  return ret;
+}
 
 std::string Config::CanonicalKey(const std::string& k) {
   // alias -> canonical name (subset of upstream's config_auto.cpp alias table that SynapseML users can reach)
@@ -32,6 +56,10 @@ std::string Config::CanonicalKey(const std::string& k) {
       {"random_seed", "seed"}, {"random_state", "seed"},
       {"num_machine", "num_machines"}, {"verbose", "verbosity"},
       {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"},
+      {"sub_feature", "feature_fraction"}, {"colsample_bytree", "feature_fraction"},
+      {"sub_feature_bynode", "feature_fraction_bynode"}, {"colsample_bynode", "feature_fraction_bynode"},
+      {"sub_row", "bagging_fraction"}, {"subsample", "bagging_fraction"}, {"bagging", "bagging_fraction"},
+      {"subsample_freq", "bagging_freq"}, {"bagging_fraction_seed", "bagging_seed"},
       {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"},
       {"cat_column", "categorical_feature"}, {"categorical_features", "categorical_feature"},
   };
@@ -92,6 +120,15 @@ void Config::Set(const std::string& params) {
   GET_B(feature_pre_filter); GET_B(use_quantized_grad); GET_I(num_grad_quant_bins); GET_B(stochastic_rounding);
   GET_B(quant_train_renew_leaf); GET_I(seed); GET_I(num_machines); GET_I(num_threads); GET_I(verbosity);
   GET_B(lambdarank_norm);
+  if (has("seed")) {      // upstream Config::Set: one LCG stream seeded with `seed` hands out the specific seeds, in this order
+    HostRandom r(seed);
+    r.NextShort(0, 32767);                          // data_random_seed (the host-side sample has its own)
+    bagging_seed = r.NextShort(0, 32767);
+    r.NextShort(0, 32767);                          // drop_seed
+    feature_fraction_seed = r.NextShort(0, 32767);
+  }
+  GET_D(feature_fraction); GET_D(feature_fraction_bynode); GET_I(feature_fraction_seed);
+  GET_D(bagging_fraction); GET_D(pos_bagging_fraction); GET_D(neg_bagging_fraction); GET_I(bagging_freq); GET_I(bagging_seed);
   // SynapseML emits the pre-3.0 key `max_position` (RankerTrainParams.scala:28).  It is honoured as an alias of
   // lambdarank_truncation_level unless that key is given explicitly (documented choice).
   if (has("lambdarank_truncation_level")) lambdarank_truncation_level = static_cast<int>(ToDouble("lambdarank_truncation_level", kv["lambdarank_truncation_level"]));

@@ -9,6 +9,19 @@
 
 namespace lgb {
 
+// Upstream's include/LightGBM/utils/random.h: a 32-bit LCG (x = 214013 x + 2531011), 15-bit and 31-bit draws.  Host only.
+struct HostRandom {
+  unsigned int x;
+  explicit HostRandom(int seed) : x(static_cast<unsigned int>(seed)) {}
+  int RandInt16() { x = 214013u * x + 2531011u; return static_cast<int>((x >> 16) & 0x7FFF); }
+  int RandInt32() { x = 214013u * x + 2531011u; return static_cast<int>(x & 0x7FFFFFFF); }
+  int NextShort(int lo, int hi) { return RandInt16() % (hi - lo) + lo; }
+  int NextInt(int lo, int hi) { return RandInt32() % (hi - lo) + lo; }
+  float NextFloat() { return static_cast<float>(RandInt16()) / 32768.0f; }
+  // K of 0..N-1, ascending (Random::Sample): sequential selection sampling for large K, Floyd's set sampling for small K
+  std::vector<int> Sample(int N, int K);
+};
+
 struct Config {
   std::string objective = "regression";
   std::string boosting = "gbdt";
@@ -33,6 +46,12 @@ struct Config {
   bool stochastic_rounding = true;
   bool quant_train_renew_leaf = false;
   int seed = 0;
+  // column / row sampling (upstream: src/treelearner/col_sampler.hpp, src/boosting/bagging.hpp).  `seed` derives the specific
+  // seeds in upstream's Config::Set order unless they are given themselves.
+  double feature_fraction = 1.0, feature_fraction_bynode = 1.0;
+  int feature_fraction_seed = 2;
+  double bagging_fraction = 1.0, pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;
+  int bagging_freq = 0, bagging_seed = 3;
   int num_machines = 1;
   int num_threads = 0;
   int verbosity = 1;

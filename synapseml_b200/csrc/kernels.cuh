@@ -252,9 +252,13 @@ __global__ void k_scales(Ctrl* ctrl, LearnerParams lp) {
 template <typename Ctrl>
 __global__ void k_quantize(const float* __restrict__ grad, const float* __restrict__ hess, int n, const Ctrl* __restrict__ ctrl,
                            LearnerParams lp, unsigned int iter, unsigned int row_offset, uint16_t* __restrict__ gh16,
-                           int2* __restrict__ ghfix) {
+                           int2* __restrict__ ghfix, const unsigned int* __restrict__ bag_bits) {
   const double inv_g = ctrl->inv_grad_scale, inv_h = ctrl->inv_hess_scale;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (bag_bits != nullptr && !((bag_bits[i >> 5] >> (i & 31)) & 1u)) {      // outside the bag: adds nothing to any histogram
+      if (lp.quantized) gh16[i] = 0; else ghfix[i] = make_int2(0, 0);
+      continue;
+    }
     const float g = grad[i], h = hess[i];
     if (lp.quantized) {
       signed char qg, qh;
@@ -272,6 +276,30 @@ __global__ void k_quantize(const float* __restrict__ grad, const float* __restri
       ghfix[i] = make_int2(__double2int_rn(g * inv_g), __double2int_rn(h * inv_h));
     }
   }
+}
+
+// Bagging (upstream src/boosting/bagging.hpp, BaggingHelper): every row draws once from the LCG stream of its 1024-row block
+// (seeded bagging_seed + block; the streams run on from one re-bagging to the next) and is in the bag when the 15-bit draw / 32768
+// is below bagging_fraction.  One thread per block; writes the bag as a bit per row and adds the bag size to *count.
+__global__ void k_bag_sample(unsigned int* __restrict__ rand_state, int n, double fraction, unsigned int* __restrict__ bits,
+                             int* __restrict__ count) {
+  const int blk = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blk >= (n + 1023) / 1024) return;
+  unsigned int x = rand_state[blk];
+  int cnt = 0;
+  for (int w = 0; w < 32; ++w) {
+    unsigned int word = 0;
+    for (int j = 0; j < 32; ++j) {
+      if (blk * 1024 + w * 32 + j < n) {
+        x = 214013u * x + 2531011u;
+        const float u = static_cast<float>((x >> 16) & 0x7FFF) / 32768.0f;
+        if (static_cast<double>(u) < fraction) { word |= 1u << j; ++cnt; }
+      }
+    }
+    bits[blk * 32 + w] = word;
+  }
+  rand_state[blk] = x;
+  atomicAdd(count, cnt);
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6 split search

@@ -79,3 +79,69 @@ def test_lambdarank_runs_and_improves_ndcg(oracle):
         tops.append(rel[m][np.argmax(s[m])])
         means.append(rel[m].mean())
     assert np.mean(tops) > np.mean(means) + 0.3
+
+
+class _Lcg:
+    """Test-side restatement of upstream's utils/random.h, independent of the oracle's C++ (x = 214013 x + 2531011 mod 2^32)."""
+
+    def __init__(self, seed):
+        self.x = seed & 0xFFFFFFFF
+
+    def _step(self):
+        self.x = (214013 * self.x + 2531011) & 0xFFFFFFFF
+        return self.x
+
+    def next_float(self):
+        return np.float32((self._step() >> 16) & 0x7FFF) / np.float32(32768.0)
+
+    def next_int(self, lo, hi):
+        return (self._step() & 0x7FFFFFFF) % (hi - lo) + lo
+
+    def sample(self, n, k):
+        if k == n:
+            return list(range(n))
+        if k > 1 and k > n / np.log2(k):
+            out = []
+            for i in range(n):
+                if float(self.next_float()) < (k - len(out)) / (n - i):
+                    out.append(i)
+            return out
+        chosen = set()
+        for r in range(n - k, n):
+            v = self.next_int(0, r)
+            chosen.add(r if v in chosen else v)
+        return sorted(chosen)
+
+
+def test_lcg_known_answers():
+    r = _Lcg(2)                                        # 214013 * 2 + 2531011 = 2959037 -> >> 16 = 45
+    assert r._step() == 2959037 and (2959037 >> 16) & 0x7FFF == 45
+    assert abs(float(_Lcg(2).next_float()) - 45 / 32768) < 1e-12
+
+
+def test_feature_fraction_draws_one_column_sample_per_tree(oracle):
+    X, y = S.higgs_shape(20000)
+    F = X.shape[1]
+    for frac, seed in ((0.6, 2), (0.1, 7)):            # 0.6: sequential selection sampling; 0.1: Floyd's set sampling (K small)
+        bst, _ = oracle.fit(X, y, PQ + " feature_fraction=%g feature_fraction_seed=%d" % (frac, seed), num_iterations=6)
+        rng = _Lcg(seed)
+        k = max(int(F * frac + 0.5), min(2, F))
+        for t in TextModel(bst.save_model_to_string()).trees:
+            allowed = set(rng.sample(F, k))
+            assert len(allowed) == k
+            assert set(t.split_feature[:t.num_leaves - 1].tolist()) <= allowed
+
+
+def test_bagging_bag_size_streams_and_out_of_bag_scores(oracle):
+    X, y = S.higgs_shape(20000 + 100)
+    n = len(y)
+    frac, freq, seed = 0.6, 2, 5
+    bst, _ = oracle.fit(X, y, PQ + " bagging_fraction=%g bagging_freq=%d bagging_seed=%d" % (frac, freq, seed), num_iterations=6)
+    m = TextModel(bst.save_model_to_string())
+    rands = [_Lcg(seed + b) for b in range((n + 1023) // 1024)]
+    for it, t in enumerate(m.trees):
+        if it % freq == 0:                             # the block streams run on from one re-bagging to the next
+            bag = sum(float(rands[i // 1024].next_float()) < frac for i in range(n))
+        assert t.internal_count[0] == bag and t.leaf_count.sum() == bag
+    assert 0.55 * n < bag < 0.65 * n
+    assert np.allclose(m.predict_raw(X), bst.scores(), rtol=0, atol=1e-12)      # every row is scored, in the bag or not
