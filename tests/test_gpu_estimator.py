@@ -104,9 +104,25 @@ def test_unsupported_options_fail_loudly(native):
     X, y = S.higgs_shape(2000)
     df = LocalDataFrame.from_arrays(X, y)
     from synapseml_b200.lightgbm.native import LightGBMNativeError
-    for kw in (dict(boostingType="dart"), dict(zeroAsMissing=True), dict(maxBin=1000)):
+    for kw in (dict(boostingType="dart"), dict(zeroAsMissing=True), dict(maxBin=1000), dict(featureFractionByNode=0.5),
+               dict(baggingFreq=1, posBaggingFraction=0.5)):
         with pytest.raises((LightGBMNativeError, NotImplementedError)):
             LightGBMClassifier(numIterations=1, **kw).fit(df)
+
+
+def test_bagging_and_feature_fraction_params_reach_the_learner(native):
+    # VerifyLightGBMClassifierStream.scala "bagging" / featureFraction settings: they change the model and are echoed in it
+    X, y = S.higgs_shape(40000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    kw = dict(numIterations=8, numLeaves=15, useQuantizedGrad=True, stochasticRounding=False, samplingMode="fixed")
+    plain = LightGBMClassifier(**kw).fit(df)
+    sampled = LightGBMClassifier(baggingFraction=0.7, baggingFreq=1, baggingSeed=3, featureFraction=0.6, **kw).fit(df)
+    again = LightGBMClassifier(baggingFraction=0.7, baggingFreq=1, baggingSeed=3, featureFraction=0.6, **kw).fit(df)
+    ms = sampled.getNativeModel()
+    assert "[bagging_fraction: 0.7]" in ms and "[feature_fraction: 0.6]" in ms and "[bagging_freq: 1]" in ms
+    assert ms == again.getNativeModel()
+    assert ms.split("parameters:")[0] != plain.getNativeModel().split("parameters:")[0]
+    assert auc(y, sampled.transform(X)["probability"][:, 1]) > 0.72
 
 
 def test_sparse_partitions_give_the_dense_model(native):
