@@ -105,7 +105,8 @@ int LGBM_DatasetFree(DatasetHandle handle);
 int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out);
 /* booster/LightGBMBooster.scala:355-365 (from TrainUtils.scala:98-135) — one boosting iteration (kernels K3-K8) */
 int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished);
-/* booster/LightGBMBooster.scala:372-392 */
+/* booster/LightGBMBooster.scala:372-392 (from TrainUtils.scala:80-86, FObjTrait): one iteration grown from the caller's gradients;
+   grad / hess are host arrays of num_data floats; no automatic initial score (upstream GBDT::TrainOneIter with gradients) */
 int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished);
 /* booster/LightGBMBooster.scala:316-323 (learning-rate schedule through the delegate) */
 int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters);
@@ -157,6 +158,9 @@ int LGBM_B200_BoosterTimerStart(BoosterHandle handle);
 int LGBM_B200_BoosterTimerStop(BoosterHandle handle, float* out_ms);
 int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_t nrow, int32_t ncol, double* out);
 
+/* booster/LightGBMBooster.scala:254-258 (TrainUtils.scala:22-24, continued training from modelString): the trees of `other_handle`
+   go in front of this booster's (upstream GBDT::MergeFrom); training scores are not changed by the merge */
+int LGBM_BoosterMerge(BoosterHandle handle, BoosterHandle other_handle);
 /* ---- validation data and metrics: what early stopping evaluates every iteration
  * (LGBM/TrainUtils.scala:137-169 through LGBM/booster/LightGBMBooster.scala:283-314; the validation dataset is created from the
  * training dataset's bin mappers, LGBM/StreamingPartitionTask.scala:154-171).  AddValidData must precede the first iteration.

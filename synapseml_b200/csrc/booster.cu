@@ -362,8 +362,10 @@ void Booster::InitObjective() {
     d_inv_max_dcg_.Alloc(nq); LGB_CUDA(cudaMemcpy(d_inv_max_dcg_.p, inv.data(), sizeof(double) * nq, cudaMemcpyHostToDevice));
     d_label_gain_.Alloc(label_gain.size()); LGB_CUDA(cudaMemcpy(d_label_gain_.p, label_gain.data(), sizeof(double) * label_gain.size(), cudaMemcpyHostToDevice));
     d_discount_.Alloc(kMaxPosition); LGB_CUDA(cudaMemcpy(d_discount_.p, discount.data(), sizeof(double) * kMaxPosition, cudaMemcpyHostToDevice));
+  } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
+    obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, regression, lambdarank)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, regression, lambdarank, custom)");
   }
 }
 
@@ -741,11 +743,24 @@ void Booster::AddConstantToValidSets(double v) {
 
 // ---------------------------------------------------------------------------------------------------- GBDT
 bool Booster::UpdateOneIter() {
+  LGB_CHECK(obj_ != kCustom, "objective=custom has no gradients of its own: call LGBM_BoosterUpdateOneIterCustom");
+  return TrainOneIter(nullptr, nullptr);
+}
+
+// GBDT::TrainOneIter(gradients, hessians) with caller-supplied gradients (upstream src/boosting/gbdt.cpp): no automatic initial
+// score, the arrays replace the objective's for this iteration, everything behind them is the same path.
+bool Booster::UpdateOneIterCustom(const float* grad, const float* hess) {
+  LGB_CHECK(grad != nullptr && hess != nullptr, "LGBM_BoosterUpdateOneIterCustom: grad / hess is null");
+  return TrainOneIter(grad, hess);
+}
+
+bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   LGB_CHECK(!predict_only_, "this booster was loaded from a model string and can only predict");
   LGB_CUDA(cudaSetDevice(device_));
   const double kEps = 1e-15f;
   double init_score = 0.0;
-  if (models_.empty() && !ds_->has_init_score && cfg_.boost_from_average && obj_ != kLambdarank) {
+  const bool custom = custom_grad != nullptr;
+  if (!custom && models_.empty() && !ds_->has_init_score && cfg_.boost_from_average && obj_ != kLambdarank) {
     double sums[2];
     BoostFromScoreLocalSums(&sums[0], &sums[1]);
     net_->HostAllReduceSum(sums, 2);
@@ -775,9 +790,12 @@ bool Booster::UpdateOneIter() {
   tree.num_leaves = 1;
   tree.leaf_value.assign(1, 0.0);
   if (need_train_ && F_ > 0) {
-    const bool fused = grad_ready_;       // produced by the previous iteration's apply-tree pass
+    const bool fused = grad_ready_ && !custom;       // produced by the previous iteration's apply-tree pass
     if (fused) grad_cur_ ^= 1;
-    else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
+    else if (custom) {       // pageable sources are staged before the calls return
+      LGB_CUDA(cudaMemcpyAsync(d_grad_[grad_cur_].p, custom_grad, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
+      LGB_CUDA(cudaMemcpyAsync(d_hess_[grad_cur_].p, custom_hess, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
+    } else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
     grad_ready_ = false;
     Bagging();
     ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
@@ -825,16 +843,13 @@ bool Booster::UpdateOneIter() {
   return false;
 }
 
-bool Booster::UpdateOneIterCustom(const float*, const float*) {
-  throw std::runtime_error("LGBM_BoosterUpdateOneIterCustom (custom objective) is not supported by this library yet");
-}
-
 ModelHeader Booster::MakeHeader() const {
   if (predict_only_) return loaded_header_;
   ModelHeader h;
   h.max_feature_idx = ds_->num_total_features - 1;
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
   else if (obj_ == kL2) h.objective = "regression";
+  else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
   h.feature_names = ds_->feature_names;
   for (int j = 0; j < ds_->num_total_features; ++j) {
@@ -885,6 +900,8 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
   } else if (o.rfind("lambdarank", 0) == 0) {
     obj_ = kLambdarank;
+  } else if (o.empty() || o.rfind("custom", 0) == 0) {
+    obj_ = kCustom;      // trained with caller-supplied gradients: predictions are raw scores
   } else {
     LGB_CHECK(o.rfind("regression", 0) == 0, "Model string: objective '%s' is not supported by this library", o.c_str());
     obj_ = kL2;
@@ -893,6 +910,17 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
   device_ = -1;      // resolved at the first prediction: loading and re-saving a model needs no GPU
   iter_ = static_cast<int>(models_.size());
   model_version_ = 1;
+}
+
+void Booster::MergeFrom(const Booster& other) {
+  LGB_CHECK(!predict_only_, "LGBM_BoosterMerge: the receiving booster must be a training booster");
+  LGB_CHECK(other.NumTotalFeatures() == NumTotalFeatures(), "LGBM_BoosterMerge: the merged model has %d features, the training data %d",
+            other.NumTotalFeatures(), NumTotalFeatures());
+  std::vector<HostTree> merged(other.models_);
+  num_init_iteration_ = static_cast<int>(merged.size());
+  for (HostTree& t : models_) merged.push_back(std::move(t));
+  models_ = std::move(merged);
+  ++model_version_;
 }
 
 int Booster::NumTotalFeatures() const { return predict_only_ ? loaded_header_.max_feature_idx + 1 : ds_->num_total_features; }

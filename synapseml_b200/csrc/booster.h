@@ -83,11 +83,13 @@ class Booster {
   explicit Booster(const std::string& model_str);
   ~Booster();
   bool UpdateOneIter();
-  bool UpdateOneIterCustom(const float* grad, const float* hess);
+  bool UpdateOneIterCustom(const float* grad, const float* hess);     // host arrays of num_data floats each
   void ResetParameter(const char* params);
   std::string SaveModelToString(int start_iteration, int num_iteration) const;
   int NumTrees() const { return static_cast<int>(models_.size()); }
-  int CurrentIteration() const { return iter_; }
+  int CurrentIteration() const { return iter_ + num_init_iteration_; }
+  // LGBM_BoosterMerge (upstream GBDT::MergeFrom): the other booster's trees go in front of this one's; scores are not touched
+  void MergeFrom(const Booster& other);
   void CopyScores(double* out) const;
   void CopyGradients(float* g, float* h) const;
   void CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const;
@@ -134,10 +136,11 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank } obj_ = kL2;
+  enum Obj { kBinary, kL2, kLambdarank, kCustom } obj_ = kL2;   // kCustom: gradients come from the caller (objective=custom)
   bool need_train_ = true, has_weights_ = false;
   double label_weights_[2] = {1.0, 1.0};
   std::vector<HostTree> models_;
+  int num_init_iteration_ = 0;           // trees merged in front (continued training)
   // scoring: the model flattened into device arrays (re-uploaded when the model changed)
   bool predict_only_ = false;
   ModelHeader loaded_header_;
@@ -189,6 +192,7 @@ class Booster {
   DevBuf<unsigned char> d_feature_mask_; // [F] this tree's column sample (feature_fraction < 1 only)
   HostRandom feature_rand_{2};           // ColSampler's stream, seeded with feature_fraction_seed
   void SampleFeaturesForTree();
+  bool TrainOneIter(const float* grad, const float* hess);
   // bagging (bagging_freq > 0, bagging_fraction < 1): the bag as a bit per row, re-drawn every bagging_freq iterations
   bool bagging_ = false;
   DevBuf<unsigned int> d_bag_bits_, d_bag_rand_;

@@ -36,7 +36,8 @@ void Booster::InitMetrics() {
       else if (ch != ' ' && ch != '"') t.push_back(ch);
     }
   }
-  if (names.empty()) names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : "ndcg");     // the objective's default
+  if (names.empty() && obj_ != kCustom)      // the objective's default; a custom objective has none
+    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : "ndcg");
   for (const std::string& m : names) {
     if (m == "None" || m == "none" || m == "null" || m == "na" || m == "custom") continue;
     if (m == "binary_logloss" || m == "binary") metrics_.push_back({kEvLogloss, "binary_logloss"});
@@ -71,7 +72,7 @@ void Booster::AddValidData(Dataset* valid) {
   LGB_CHECK(valid->num_total_features == ds_->num_total_features && valid->num_features() == ds_->num_features(),
             "AddValidData: the validation dataset was not created from the training dataset's bin mappers");
   LGB_CHECK(valid->device == device_, "AddValidData: the validation dataset lives on another GPU");
-  LGB_CHECK(models_.empty(), "AddValidData must be called before the first iteration");
+  LGB_CHECK(iter_ == 0 && static_cast<int>(models_.size()) == num_init_iteration_, "AddValidData must be called before the first iteration");
   LGB_CUDA(cudaSetDevice(device_));
   valids_.emplace_back();
   ValidSet& v = valids_.back();

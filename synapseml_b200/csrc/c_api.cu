@@ -411,6 +411,12 @@ int LGBM_B200_BoosterPredictRaw(BoosterHandle handle, const double* data, int32_
 }
 
 // ---- validation data + metrics
+int LGBM_BoosterMerge(BoosterHandle handle, BoosterHandle other_handle) {
+  API_BEGIN();
+  LGB_CHECK(handle != nullptr && other_handle != nullptr, "LGBM_BoosterMerge: null booster handle");
+  static_cast<Booster*>(handle)->MergeFrom(*static_cast<const Booster*>(other_handle));
+  API_END();
+}
 int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data) {
   API_BEGIN();
   Dataset* v = static_cast<Dataset*>(const_cast<void*>(valid_data));

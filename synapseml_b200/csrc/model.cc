@@ -100,7 +100,7 @@ std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& tre
   if (num_iteration > 0) last = std::min(last, first + num_iteration);
   std::string s = "tree\nversion=v3\nnum_class=1\nnum_tree_per_iteration=1\nlabel_index=0\n";
   s += "max_feature_idx=" + std::to_string(h.max_feature_idx) + "\n";
-  s += "objective=" + h.objective + "\n";
+  if (!h.objective.empty()) s += "objective=" + h.objective + "\n";
   s += "feature_names=";
   for (size_t j = 0; j < h.feature_names.size(); ++j) { if (j) s.push_back(' '); s += h.feature_names[j]; }
   s += "\nfeature_infos=";

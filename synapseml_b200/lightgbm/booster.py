@@ -18,6 +18,7 @@ class LightGBMBooster:
             h = C.c_void_p()
             validate(lightgbmlib().LGBM_BoosterCreate(training_dataset.dataset_ptr, parameters.encode(), C.byref(h)), "Booster")
             self.booster_handle = h
+            self.train_dataset = training_dataset
             self._train_rows = training_dataset.num_data()
         elif model_str is not None:
             # LightGBMBooster(modelStr): the booster is rebuilt from the model string where it is needed (:41-49)
@@ -60,6 +61,29 @@ class LightGBMBooster:
     def update_one_iteration(self):
         fin = C.c_int()
         validate(lightgbmlib().LGBM_BoosterUpdateOneIter(self.booster_handle, C.byref(fin)), "Booster Update One Iter")
+        self.is_finished = fin.value == 1
+        return self.is_finished
+
+    def merge_booster(self, model):
+        """mergeBooster (:254-258): the trees of the serialized model go in front of this booster's (continued training)."""
+        other, n_iter = C.c_void_p(), C.c_int()
+        lib = lightgbmlib()
+        validate(lib.LGBM_BoosterLoadModelFromString(model.encode(), C.byref(n_iter), C.byref(other)), "Booster LoadFromString")
+        try:
+            validate(lib.LGBM_BoosterMerge(self.booster_handle, other), "Booster Merge")
+        finally:
+            lib.LGBM_BoosterFree(other)
+
+    def update_one_iteration_custom(self, gradient, hessian):
+        """updateOneIterationCustom (:371-392): one iteration from caller-supplied gradients (float32, one per training row)."""
+        g = np.ascontiguousarray(gradient, dtype=np.float32)
+        h = np.ascontiguousarray(hessian, dtype=np.float32)
+        if len(g) != self._train_rows or len(h) != self._train_rows:
+            raise ValueError("gradient / hessian must have one value per training row (%d)" % self._train_rows)
+        fin = C.c_int()
+        validate(lightgbmlib().LGBM_BoosterUpdateOneIterCustom(self.booster_handle, g.ctypes.data_as(C.POINTER(C.c_float)),
+                                                               h.ctypes.data_as(C.POINTER(C.c_float)), C.byref(fin)),
+                 "Booster Update One Iter Custom")
         self.is_finished = fin.value == 1
         return self.is_finished
 

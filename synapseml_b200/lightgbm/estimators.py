@@ -70,6 +70,7 @@ _DEFAULTS = dict(
     labelCol="label", featuresCol="features", weightCol=None, initScoreCol=None, slotNames=None, referenceDataset=None,
     useQuantizedGrad=None, numGradQuantBins=None, stochasticRounding=None, isProvideTrainingMetric=None, delegate=None, validationIndicatorCol=None,
     defaultListenPort=nm.DEFAULT_LOCAL_LISTEN_PORT, timeout=1200.0, modelString=None,
+    fobj=None,      # FObjTrait: an object with get_gradient(predictions [n][1], training_dataset) -> (grad f32[n], hess f32[n])
 )
 _SPARK_DEFAULTS = dict(maxBin=255, binSampleCount=200000, minDataInLeaf=20, numLeaves=31)   # values getXxx returns when unset
 
@@ -134,7 +135,7 @@ class LightGBMBase:
             dartModeParams=DartModeParams(),
             executionParams=ExecutionParams(g["chunkSize"], g["matrixType"], exec_threads, g["dataTransferMode"], g["samplingMode"],
                                             g["samplingSubsetSize"], g["microBatchSize"], g["useSingleDatasetMode"], g["maxStreamingOMPThreads"]),
-            objectiveParams=ObjectiveParams(g["objective"], None),
+            objectiveParams=ObjectiveParams(g["objective"], g["fobj"]),
             seedParams=SeedParams(seed=g["seed"], deterministic=g["deterministic"], dataRandomSeed=g["dataRandomSeed"],
                                   boostingType=g["boostingType"], objective=g["objective"]),
             categoricalParams=CategoricalParams(),

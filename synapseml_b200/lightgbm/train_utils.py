@@ -9,17 +9,20 @@ log = logging.getLogger("synapseml_b200.lightgbm")
 
 
 def create_booster(train_params, train_dataset):
-    """TrainUtils.createBooster: one native booster over the executor's dataset (modelString merge: later row)."""
-    if train_params.generalParams.modelString:
-        raise NotImplementedError("continued training from modelString (LGBM_BoosterMerge) is not built yet")
-    return LightGBMBooster(train_dataset, train_params.to_string())
+    """TrainUtils.createBooster: one native booster over the executor's dataset (+ the trees of modelString in front, when given)."""
+    booster = LightGBMBooster(train_dataset, train_params.to_string())
+    if train_params.generalParams.modelString:       # TrainUtils.scala:22-24
+        booster.merge_booster(train_params.generalParams.modelString)
+    return booster
 
 
 def update_one_iteration(train_params, booster, cur_iters):
     """TrainUtils.updateOneIteration: a native failure ends training quietly (TrainUtils.scala:89-95) but is logged loudly."""
     try:
-        if train_params.objectiveParams.fobj is not None:
-            raise NotImplementedError("custom objective (LGBM_BoosterUpdateOneIterCustom) is not built yet")
+        fobj = train_params.objectiveParams.fobj
+        if fobj is not None:       # TrainUtils.scala:80-86: raw training scores -> user gradients -> UpdateOneIterCustom
+            gradient, hessian = fobj.get_gradient(booster.inner_predict(0).reshape(-1, 1), booster.train_dataset)
+            return booster.update_one_iteration_custom(gradient, hessian)
         return booster.update_one_iteration()
     except Exception as e:  # noqa: BLE001 - mirrors the reference's catch-all
         log.warning("LightGBM reached early termination on one task, stopping training on task. "

@@ -1,0 +1,77 @@
+"""Custom objective (TrainUtils.scala:80-86, LightGBMBooster.scala:331-392): LGBM_BoosterGetPredict hands
+the raw training scores out, LGBM_BoosterUpdateOneIterCustom takes the caller's gradients.  Fed with the gradients the built-in
+objective computed, the custom path must grow the very same trees."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from helpers import NativeBooster, NativeDataset
+from synapseml_b200.data import synthetic as S
+from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LocalDataFrame
+from synapseml_b200.lightgbm.model_text import TextModel
+from synapseml_b200.lightgbm.native import validate
+
+pytestmark = pytest.mark.gpu
+
+
+def update_custom(nb, g, h):
+    fin = C.c_int()
+    validate(nb.lib.LGBM_BoosterUpdateOneIterCustom(nb.handle, g.ctypes.data_as(C.POINTER(C.c_float)), h.ctypes.data_as(C.POINTER(C.c_float)),
+                                                    C.byref(fin)))
+    return fin.value == 1
+
+
+def tree_blocks(model_str):
+    return model_str.split("end of trees")[0].split("Tree=0\n", 1)[1]
+
+
+@pytest.mark.parametrize("mode", ["quantized", "float"])
+def test_builtin_gradients_through_the_custom_entry_point_grow_the_same_trees(native, mode):
+    X, y = S.higgs_shape(50000)
+    common = " num_leaves=31 max_bin=63 min_data_in_leaf=20 boost_from_average=false verbosity=-1"
+    if mode == "quantized":
+        common += " use_quantized_grad=true stochastic_rounding=false"
+    nd = NativeDataset(X, y, "objective=binary" + common)
+    a = NativeBooster(nd, "objective=binary" + common)
+    b = NativeBooster(nd, "objective=custom" + common)
+    for _ in range(8):
+        assert not a.update()
+        g, h = a.gradients()                    # the gradients this iteration of `a` was grown from
+        assert not update_custom(b, g, h)
+    ma, mb = a.model(), b.model()
+    assert tree_blocks(ma) == tree_blocks(mb)
+    assert np.array_equal(a.scores(), b.scores())
+    assert "objective=binary" in ma and "\nobjective=" not in mb.split("Tree=0")[0]      # no objective function, no objective line
+    with pytest.raises(Exception):               # a custom-objective booster has no gradients of its own
+        b.update()
+    a.free()
+    b.free()
+    nd.free()
+
+
+class LogLikelihood:
+    """The reference test's FObjTrait (VerifyLightGBMClassifierStream.scala:57-72)."""
+
+    def get_gradient(self, predictions, training_data):
+        labels = training_data.get_label()
+        prob = 1.0 / (1.0 + np.exp(-predictions[:, 0]))
+        return (prob - labels).astype(np.float32), (prob * (1.0 - prob)).astype(np.float32)
+
+
+def test_estimator_with_fobj_learns_and_scores_raw(native):
+    X, y = S.higgs_shape(40000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=1)
+    model = LightGBMClassifier(numIterations=30, numLeaves=15, fobj=LogLikelihood()).fit(df)
+    ms = model.getNativeModel()
+    assert "[objective: custom]" in ms and len(TextModel(ms).trees) == 30
+    raw = TextModel(ms).predict_raw(X)
+    order = np.argsort(raw, kind="stable")
+    r = np.empty(len(raw)); r[order] = np.arange(1, len(raw) + 1)
+    pos = y > 0
+    auc = (r[pos].sum() - pos.sum() * (pos.sum() + 1) / 2) / (pos.sum() * (~pos).sum())
+    assert auc > 0.75
+    builtin = LightGBMClassifier(numIterations=30, numLeaves=15).fit(df)
+    # same loss, same data: the custom model tracks the built-in one (it starts from 0 instead of the label average)
+    rb = TextModel(builtin.getNativeModel()).predict_raw(X)
+    assert np.corrcoef(raw, rb)[0, 1] > 0.98
