@@ -27,10 +27,11 @@ def main():
     lo, hi = n * rank // world, n * (rank + 1) // world
     X, y = S.higgs_shape(hi - lo, start=lo)
     ok = True
-    for quant in (True, False):
+    sampling = dict(baggingFraction=0.7, baggingFreq=1, featureFraction=0.7)      # every rank bags its own rows, all draw the same columns
+    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling))):
         est = LightGBMClassifier(numIterations=iters, numLeaves=31, maxBin=63, useQuantizedGrad=quant, stochasticRounding=False,
                                  samplingMode="fixed", microBatchSize=8192, binSampleCount=50000,
-                                 defaultListenPort=12400 + (os.getpid() % 1000) * 8 + (0 if quant else 4))
+                                 defaultListenPort=12400 + (os.getpid() % 1000) * 12 + case * 4, **extra)
         model = est.fit(LocalDataFrame.from_arrays(X, y, num_partitions=2))
         if rank == 0:
             from oracle import oracle as O
@@ -41,7 +42,7 @@ def main():
             ours, theirs = strip_parameters(model.model_str), strip_parameters(bst.save_model_to_string())
             if quant:
                 same = ours == theirs
-                print("quantized dp%d model identical to oracle: %s" % (world, same), flush=True)
+                print("quantized%s dp%d model identical to oracle: %s" % (" sampled" if extra else "", world, same), flush=True)
                 ok &= same
             else:
                 from synapseml_b200.lightgbm.model_text import TextModel

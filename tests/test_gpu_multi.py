@@ -26,4 +26,5 @@ def test_two_gpu_data_parallel_matches_oracle(native, exchange):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "quantized dp2 model identical to oracle: True" in r.stdout
+    assert "quantized sampled dp2 model identical to oracle: True" in r.stdout
     assert ("exchange over peer memory" in r.stderr) == (exchange == "peer"), r.stderr[-2000:]
