@@ -192,9 +192,12 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       const int k = i / (LPR * kBins);
       const int f = tile * FT + qq * BPL + k;
       long long g = 0, h = 0;
+      // a warp covers R consecutive bins x LPR lanes; all bins share the banks of a given (sub-histogram, lane), so each thread
+      // starts at a different sub-histogram ((bin + rr) mod R): 32 distinct banks per access instead of an R-way conflict
+      const int skew = (i / LPR) & (R - 1);
       #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
-        const int a = bin * 32 + rr * LPR + qq;
+        const int a = bin * 32 + ((rr + skew) & (R - 1)) * LPR + qq;
         if (FLT) {
           g += static_cast<int>(hsm[(2 * k) * (kBins * 32) + a]);
           h += static_cast<int>(hsm[(2 * k + 1) * (kBins * 32) + a]);

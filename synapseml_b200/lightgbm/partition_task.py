@@ -66,6 +66,7 @@ class BasePartitionTask:
                 measures["train_scores"] = booster.inner_predict(0)
             return model_str
         finally:
+            t0 = time.time()
             if booster is not None:
                 booster.free_native_memory()
             if valid_ds is not None:
@@ -73,6 +74,7 @@ class BasePartitionTask:
             dataset.close()
             if info is not None and info.world > 1:
                 nm.free_lightgbm_network()
+            measures["cleanupTime"] = time.time() - t0      # freeing the booster's and the dataset's device / pinned memory
 
 
 class StreamingPartitionTask(BasePartitionTask):
