@@ -94,7 +94,9 @@ struct BatchCtrl {
   const unsigned int* bag_bits;
 };
 
+__constant__ int c_trace_on;      // set by the host while LGB_B200_TRACE records a tree
 __device__ __forceinline__ void Trace(BatchCtrl* ctrl, int id) {
+  if (!c_trace_on) return;      // a constant-bank read: the disabled case must not put a global load on thread 0's critical path
   if (ctrl->trace == nullptr) return;
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));

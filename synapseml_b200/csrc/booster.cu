@@ -611,6 +611,8 @@ void Booster::TrainTree(HostTree* out) {
   if (trace_cap_ > 0) {      // trace three trees starting at iteration LGB_B200_TRACE_FROM
     long long* p = (iter_ >= trace_from_ && iter_ < trace_from_ + 3) ? d_trace_.p : nullptr;
     LGB_CUDA(cudaMemcpyAsync(&d_ctrl_->trace, &p, sizeof(p), cudaMemcpyHostToDevice, stream_));
+    const int on = p != nullptr ? 1 : 0;
+    LGB_CUDA(cudaMemcpyToSymbolAsync(c_trace_on, &on, sizeof(int), 0, cudaMemcpyHostToDevice, stream_));
     LGB_CUDA(cudaStreamSynchronize(stream_));
   }
   if (lp_.feature_mask != nullptr) SampleFeaturesForTree();
