@@ -177,6 +177,8 @@ struct Config {
   bool quant_train_renew_leaf = false;
   int seed = 0;
   // column / row sampling (upstream config.h defaults); `seed` derives the specific seeds (Config::Set, upstream src/io/config.cpp)
+  // regression objectives beyond L2 (upstream config.h defaults)
+  double alpha = 0.9, fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;
   double feature_fraction = 1.0;
   int feature_fraction_seed = 2;
   double bagging_fraction = 1.0;
@@ -296,6 +298,10 @@ struct Config {
       r.NextShort(0, int_max);                       // drop_seed
       feature_fraction_seed = r.NextShort(0, int_max);
     }
+    getd("alpha", &alpha);
+    getd("fair_c", &fair_c);
+    getd("poisson_max_delta_step", &poisson_max_delta_step);
+    getd("tweedie_variance_power", &tweedie_variance_power);
     getd("feature_fraction", &feature_fraction);
     geti("feature_fraction_seed", &feature_fraction_seed);
     getd("bagging_fraction", &bagging_fraction);

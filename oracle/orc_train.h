@@ -260,7 +260,9 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE } obj = OBJ_L2;
+  bool IsPointRegression() const { return obj == OBJ_L2 || obj >= OBJ_HUBER; }
+  bool LogLink() const { return obj == OBJ_POISSON || obj == OBJ_GAMMA || obj == OBJ_TWEEDIE; }
   bool need_train = true;
   double label_weights[2] = {1.0, 1.0};
   bool has_weights = false;
@@ -366,6 +368,14 @@ class Booster {
       label_weights[1] *= cfg.scale_pos_weight;
     } else if (cfg.objective == "regression") {
       obj = OBJ_L2;
+    } else if (cfg.objective == "huber") {
+      obj = OBJ_HUBER;
+    } else if (cfg.objective == "fair") {
+      obj = OBJ_FAIR;
+    } else if (cfg.objective == "poisson" || cfg.objective == "gamma" || cfg.objective == "tweedie") {
+      obj = cfg.objective == "poisson" ? OBJ_POISSON : cfg.objective == "gamma" ? OBJ_GAMMA : OBJ_TWEEDIE;
+      for (auto& sh : shards) for (float l : sh.ds->label)      // RegressionPoissonLoss::Init / Gamma: label domain
+        if (l < 0.0f || (obj == OBJ_GAMMA && l <= 0.0f)) throw std::runtime_error("oracle: " + cfg.objective + " needs non-negative labels");
     } else if (cfg.objective == "lambdarank") {
       obj = OBJ_LAMBDARANK;
       label_gain = cfg.label_gain;
@@ -434,13 +444,15 @@ class Booster {
       pavg = std::max<double>(pavg, kEpsilon);
       return std::log(pavg / (1.0f - pavg)) / cfg.sigmoid;
     }
-    if (obj == OBJ_L2) {
+    if (IsPointRegression()) {
       for (auto& sh : shards) {
         const Dataset* d = sh.ds;
         if (has_weights) { for (int64_t i = 0; i < d->num_data; ++i) { suml += d->label[i] * d->weight[i]; sumw += d->weight[i]; } }
         else { sumw += static_cast<double>(d->num_data); for (int64_t i = 0; i < d->num_data; ++i) suml += d->label[i]; }
       }
-      return suml / sumw;
+      const double mean = suml / sumw;
+      if (LogLink()) return mean > 0.0 ? std::log(mean) : -std::numeric_limits<double>::infinity();      // Common::SafeLog
+      return mean;
     }
     return 0.0;
   }
@@ -478,6 +490,40 @@ class Booster {
             sh.grad[i] = static_cast<score_t>(static_cast<score_t>(sh.score[i] - d->label[i]) * d->weight[i]);
             sh.hess[i] = static_cast<score_t>(d->weight[i]);
           }
+        }
+      } else if (obj != OBJ_LAMBDARANK) {
+        // regression_objective.hpp: Huber (alpha), Fair (fair_c), Poisson (poisson_max_delta_step), Gamma, Tweedie (rho); exp is the
+        // software exp shared with the CUDA library
+        const double alpha = cfg.alpha, c = cfg.fair_c, rho = cfg.tweedie_variance_power;
+        const double exp_mds = SoftExp(cfg.poisson_max_delta_step);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+          const double sc = sh.score[i];
+          const double y = d->label[i];
+          double g, h;
+          if (obj == OBJ_HUBER) {
+            const double diff = sc - y;
+            g = std::fabs(diff) <= alpha ? diff : ((diff > 0) - (diff < 0)) * alpha;
+            h = 1.0;
+          } else if (obj == OBJ_FAIR) {
+            const double x = sc - y;
+            g = c * x / (std::fabs(x) + c);
+            h = c * c / ((std::fabs(x) + c) * (std::fabs(x) + c));
+          } else if (obj == OBJ_POISSON) {
+            const double e = SoftExp(sc);
+            g = e - y;
+            h = e * exp_mds;
+          } else if (obj == OBJ_GAMMA) {
+            const double e = SoftExp(-sc);
+            g = 1.0 - y * e;
+            h = y * e;
+          } else {
+            const double e1 = SoftExp((1 - rho) * sc), e2 = SoftExp((2 - rho) * sc);
+            g = -y * e1 + e2;
+            h = -y * (1 - rho) * e1 + (2 - rho) * e2;
+          }
+          if (!has_weights) { sh.grad[i] = static_cast<score_t>(g); sh.hess[i] = static_cast<score_t>(h); }
+          else { sh.grad[i] = static_cast<score_t>(g * d->weight[i]); sh.hess[i] = static_cast<score_t>(h * d->weight[i]); }
         }
       } else {
         const int nq = static_cast<int>(d->query_boundaries.size()) - 1;
@@ -840,6 +886,7 @@ class Booster {
   std::string ObjectiveString() const {
     if (obj == OBJ_BINARY) return "binary sigmoid:" + FmtG(cfg.sigmoid);
     if (obj == OBJ_L2) return "regression";
+    if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }
 

@@ -362,6 +362,18 @@ void Booster::InitObjective() {
     d_inv_max_dcg_.Alloc(nq); LGB_CUDA(cudaMemcpy(d_inv_max_dcg_.p, inv.data(), sizeof(double) * nq, cudaMemcpyHostToDevice));
     d_label_gain_.Alloc(label_gain.size()); LGB_CUDA(cudaMemcpy(d_label_gain_.p, label_gain.data(), sizeof(double) * label_gain.size(), cudaMemcpyHostToDevice));
     d_discount_.Alloc(kMaxPosition); LGB_CUDA(cudaMemcpy(d_discount_.p, discount.data(), sizeof(double) * kMaxPosition, cudaMemcpyHostToDevice));
+  } else if (cfg_.objective == "huber" || cfg_.objective == "fair" || cfg_.objective == "poisson" || cfg_.objective == "gamma" ||
+             cfg_.objective == "tweedie") {
+    const std::string& o = cfg_.objective;
+    obj_ = o == "huber" ? kHuber : o == "fair" ? kFair : o == "poisson" ? kPoisson : o == "gamma" ? kGamma : kTweedie;
+    if (LogLink()) {      // RegressionPoissonLoss::Init: the label domain of the log-link objectives
+      double bad = 0.0, sum = 0.0;
+      for (float l : label) { bad += (l < 0.0f || (obj_ == kGamma && l <= 0.0f)); sum += l; }
+      double acc[2] = {bad, sum};
+      net_->HostAllReduceSum(acc, 2);
+      LGB_CHECK(acc[0] == 0.0, "objective=%s needs %s labels", o.c_str(), obj_ == kGamma ? "positive" : "non-negative");
+      LGB_CHECK(acc[1] > 0.0, "objective=%s: the sum of the labels is zero", o.c_str());
+    }
   } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
     obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
   } else {
@@ -392,6 +404,10 @@ void Booster::ComputeGradients() {
     k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
     k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
+  } else if (obj_ >= kHuber) {
+    const double p0 = obj_ == kHuber ? cfg_.alpha : obj_ == kFair ? cfg_.fair_c : obj_ == kPoisson ? SoftExp(cfg_.poisson_max_delta_step)
+                      : cfg_.tweedie_variance_power;
+    k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0);
   } else {
     LambdarankArgs a;
     a.score = d_score_.p; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
@@ -774,6 +790,7 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
       v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
     } else {
       v = sums[0] / sums[1];
+      if (LogLink()) v = v > 0.0 ? std::log(v) : -std::numeric_limits<double>::infinity();      // Common::SafeLog of the mean label
     }
     if (net_->active()) {   // ObtainAutomaticInitialScore: mean over machines of identical values
       double acc = 0.0;
@@ -851,6 +868,7 @@ ModelHeader Booster::MakeHeader() const {
   h.max_feature_idx = ds_->num_total_features - 1;
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
   else if (obj_ == kL2) h.objective = "regression";
+  else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
   else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
   h.feature_names = ds_->feature_names;
@@ -902,6 +920,9 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
   } else if (o.rfind("lambdarank", 0) == 0) {
     obj_ = kLambdarank;
+  } else if (o == "huber" || o == "fair" || o == "poisson" || o == "gamma" || o == "tweedie") {
+    obj_ = o == "huber" ? kHuber : o == "fair" ? kFair : o == "poisson" ? kPoisson : o == "gamma" ? kGamma : kTweedie;
+    cfg_.objective = o;
   } else if (o.empty() || o.rfind("custom", 0) == 0) {
     obj_ = kCustom;      // trained with caller-supplied gradients: predictions are raw scores
   } else {
@@ -1001,7 +1022,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
   dp_in_.Reserve(static_cast<size_t>(chunk_rows) * ncol * esz);
   dp_out_.Reserve(static_cast<size_t>(chunk_rows) * per_row);
-  const int sig_on = obj_ == kBinary ? 1 : 0;
+  const int sig_on = obj_ == kBinary ? 1 : LogLink() ? 2 : 0;      // ConvertOutput: sigmoid, exp, or none
   for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
     const int64_t nr = std::min(chunk_rows, nrow - r0);
     const unsigned char* src = static_cast<const unsigned char*>(data) + (row_major ? static_cast<size_t>(r0) * ncol * esz : 0);

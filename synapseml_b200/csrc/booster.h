@@ -136,7 +136,10 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank, kCustom } obj_ = kL2;   // kCustom: gradients come from the caller (objective=custom)
+  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie } obj_ = kL2;
+  bool PointRegression() const { return obj_ == kL2 || obj_ >= kHuber; }
+  bool LogLink() const { return obj_ == kPoisson || obj_ == kGamma || obj_ == kTweedie; }      // predictions are exp(raw score)
+  // kCustom: gradients come from the caller (objective=custom); kHuber.. : upstream regression_objective.hpp
   bool need_train_ = true, has_weights_ = false;
   double label_weights_[2] = {1.0, 1.0};
   std::vector<HostTree> models_;

@@ -17,7 +17,8 @@ namespace lgb {
 
 namespace {
 constexpr int kNumSms = 148;
-enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5 };   // (Booster has its own kL2: distinct names)
+enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
+       kEvTweedie = 10 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -37,7 +38,7 @@ void Booster::InitMetrics() {
     }
   }
   if (names.empty() && obj_ != kCustom)      // the objective's default; a custom objective has none
-    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : "ndcg");
+    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : cfg_.objective);
   for (const std::string& m : names) {
     if (m == "None" || m == "none" || m == "null" || m == "na" || m == "custom") continue;
     if (m == "binary_logloss" || m == "binary") metrics_.push_back({kEvLogloss, "binary_logloss"});
@@ -45,6 +46,11 @@ void Booster::InitMetrics() {
     else if (m == "auc") metrics_.push_back({kEvAuc, "auc"});
     else if (m == "l2" || m == "mse" || m == "mean_squared_error" || m == "regression" || m == "regression_l2") metrics_.push_back({kEvL2, "l2"});
     else if (m == "rmse" || m == "root_mean_squared_error" || m == "l2_root") metrics_.push_back({kEvRmse, "rmse"});
+    else if (m == "huber") metrics_.push_back({kEvHuber, "huber"});
+    else if (m == "fair") metrics_.push_back({kEvFair, "fair"});
+    else if (m == "poisson") metrics_.push_back({kEvPoisson, "poisson"});
+    else if (m == "gamma") metrics_.push_back({kEvGamma, "gamma"});
+    else if (m == "tweedie") metrics_.push_back({kEvTweedie, "tweedie"});
     else if (m == "ndcg" || m == "lambdarank" || m == "rank_xendcg" || m == "xendcg") {
       std::vector<int> at = cfg_.eval_at;
       if (at.empty()) at = {1, 2, 3, 4, 5};
@@ -153,9 +159,12 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
   double h[kMaxEvalAt + 2];
   bool ndcg_done = false;
   for (const MetricSpec& m : metrics_) {
-    if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse) {
-      const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError : kMetricL2;
-      k_metric_point<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, kind, cfg_.sigmoid, d_mpart_.p);
+    if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || m.kind >= kEvHuber) {
+      const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError
+                       : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;
+      const double p0 = m.kind == kEvHuber ? cfg_.alpha : m.kind == kEvFair ? cfg_.fair_c : cfg_.tweedie_variance_power;
+      k_metric_point<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, kind, cfg_.sigmoid, d_mpart_.p,
+                                                                    LogLink() ? 1 : 0, p0);
       k_metric_final<<<1, kMetricThreads, 0, stream_>>>(d_mpart_.p, kMetricBlocks, d_mout_.p);
       LGB_CUDA(cudaMemcpyAsync(h, d_mout_.p, sizeof(double) * 2, cudaMemcpyDeviceToHost, stream_));
       LGB_CUDA(cudaStreamSynchronize(stream_));

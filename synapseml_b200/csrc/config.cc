@@ -127,6 +127,7 @@ void Config::Set(const std::string& params) {
     r.NextShort(0, 32767);                          // drop_seed
     feature_fraction_seed = r.NextShort(0, 32767);
   }
+  GET_D(alpha); GET_D(fair_c); GET_D(poisson_max_delta_step); GET_D(tweedie_variance_power);
   GET_D(feature_fraction); GET_D(feature_fraction_bynode); GET_I(feature_fraction_seed);
   GET_D(bagging_fraction); GET_D(pos_bagging_fraction); GET_D(neg_bagging_fraction); GET_I(bagging_freq); GET_I(bagging_seed);
   // SynapseML emits the pre-3.0 key `max_position` (RankerTrainParams.scala:28).  It is honoured as an alias of

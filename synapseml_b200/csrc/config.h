@@ -48,6 +48,7 @@ struct Config {
   int seed = 0;
   // column / row sampling (upstream: src/treelearner/col_sampler.hpp, src/boosting/bagging.hpp).  `seed` derives the specific
   // seeds in upstream's Config::Set order unless they are given themselves.
+  double alpha = 0.9, fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;      // huber / fair / poisson / tweedie
   double feature_fraction = 1.0, feature_fraction_bynode = 1.0;
   int feature_fraction_seed = 2;
   double bagging_fraction = 1.0, pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;

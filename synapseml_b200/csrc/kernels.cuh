@@ -70,6 +70,40 @@ __global__ void k_grad_l2(const double* __restrict__ score, const float* __restr
     GradL2Row(score[i], label[i], weight != nullptr, weight ? weight[i] : 0.0f, grad + i, hess + i);
 }
 
+// Huber / Fair / Poisson / Gamma / Tweedie (upstream regression_objective.hpp); kind = Booster::Obj.  p0: alpha | fair_c |
+// exp(poisson_max_delta_step) | - | tweedie_variance_power.
+__global__ void k_grad_point(int kind, const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
+                             float* __restrict__ grad, float* __restrict__ hess, int n, double p0) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double sc = score[i];
+    const double y = label[i];
+    double g, h;
+    if (kind == 4) {            // huber
+      const double diff = sc - y;
+      g = fabs(diff) <= p0 ? diff : SignD(diff) * p0;
+      h = 1.0;
+    } else if (kind == 5) {     // fair
+      const double x = sc - y;
+      g = p0 * x / (fabs(x) + p0);
+      h = p0 * p0 / ((fabs(x) + p0) * (fabs(x) + p0));
+    } else if (kind == 6) {     // poisson
+      const double e = SoftExp(sc);
+      g = e - y;
+      h = e * p0;
+    } else if (kind == 7) {     // gamma
+      const double e = SoftExp(-sc);
+      g = 1.0 - y * e;
+      h = y * e;
+    } else {                    // tweedie
+      const double e1 = SoftExp((1 - p0) * sc), e2 = SoftExp((2 - p0) * sc);
+      g = -y * e1 + e2;
+      h = -y * (1 - p0) * e1 + (2 - p0) * e2;
+    }
+    if (weight == nullptr) { grad[i] = static_cast<float>(g); hess[i] = static_cast<float>(h); }
+    else { grad[i] = static_cast<float>(g * weight[i]); hess[i] = static_cast<float>(h * weight[i]); }
+  }
+}
+
 // LambdaRank-NDCG.  One CTA per query.  Step 1: stable rank of every document by score (descending) by counting, which
 // equals std::stable_sort's order.  Step 2 (k_grad_lambdarank): the pair loop, with every floating-point sum taken in the
 // sequential loop's order so float32 lambdas / hessians and the double sum behind the log2 normalisation are bit-identical.

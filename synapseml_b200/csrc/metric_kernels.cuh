@@ -16,7 +16,8 @@ __global__ void k_iota(int* p, int n) {
 constexpr int kMetricBlocks = 592;
 constexpr int kMetricThreads = 256;
 
-enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2 };
+enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2, kMetricHuber = 3, kMetricFair = 4, kMetricPoisson = 5,
+                   kMetricGamma = 6, kMetricTweedie = 7 };
 
 __device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -31,7 +32,7 @@ __device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
 // partial[b] = (sum loss * w, sum w) over the rows of CTA b
 __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* __restrict__ score, const float* __restrict__ label,
                                                                   const float* __restrict__ weight, long long n, int kind, double sigmoid,
-                                                                  double2* __restrict__ partial) {
+                                                                  double2* __restrict__ partial, int exp_link = 0, double p0 = 0.0) {
   __shared__ double s_w[8];
   const double kEps = (double)1e-15f;
   double sl = 0.0, sw = 0.0;
@@ -40,9 +41,33 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
     const float y = label[i];
     const double w = weight ? static_cast<double>(weight[i]) : 1.0;
     double loss;
-    if (kind == kMetricL2) {
-      const double d = s - static_cast<double>(y);
-      loss = d * d;
+    if (kind >= kMetricL2) {
+      // regression_metric.hpp: the loss sees the objective's converted output (exp for the log-link objectives)
+      const double t = exp_link ? exp(s) : s;
+      const double lab = static_cast<double>(y);
+      if (kind == kMetricL2) {
+        const double d = t - lab;
+        loss = d * d;
+      } else if (kind == kMetricHuber) {          // p0 = alpha
+        const double d = t - lab;
+        loss = fabs(d) <= p0 ? 0.5 * d * d : p0 * (fabs(d) - 0.5 * p0);
+      } else if (kind == kMetricFair) {           // p0 = fair_c
+        const double x = fabs(t - lab);
+        loss = p0 * x - p0 * p0 * log1p(x / p0);
+      } else if (kind == kMetricPoisson) {
+        const double sc = t < 1e-10 ? 1e-10 : t;
+        loss = sc - lab * log(sc);
+      } else if (kind == kMetricGamma) {          // psi = 1: -((label * theta - b) / a + c), theta = -1 / score
+        const double theta = -1.0 / t;
+        const double b = -((-theta) > 0.0 ? log(-theta) : -INFINITY);
+        const double c = (lab > 0.0 ? log(lab) : -INFINITY) - (lab > 0.0 ? log(lab) : -INFINITY);
+        loss = -((lab * theta - b) + c);
+      } else {                                    // tweedie, p0 = rho
+        const double sc = t < 1e-10 ? 1e-10 : t;
+        const double a = lab * exp((1 - p0) * log(sc)) / (1 - p0);
+        const double b = exp((2 - p0) * log(sc)) / (2 - p0);
+        loss = -a + b;
+      }
     } else {
       const double prob = 1.0 / (1.0 + exp(-sigmoid * s));
       if (kind == kMetricBinaryLogloss) {

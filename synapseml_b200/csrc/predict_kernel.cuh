@@ -58,7 +58,8 @@ __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long 
       else acc += m.leaf_value[lo + leaf];
     }
     if (mode != kPredictLeaf) {
-      if (mode == kPredictNormal && sigmoid_on) acc = 1.0 / (1.0 + SoftExp(-sigmoid * acc));
+      if (mode == kPredictNormal && sigmoid_on == 1) acc = 1.0 / (1.0 + SoftExp(-sigmoid * acc));
+      else if (mode == kPredictNormal && sigmoid_on == 2) acc = SoftExp(acc);      // log-link regression objectives
       out[r] = acc;
     }
   }

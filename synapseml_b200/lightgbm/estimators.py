@@ -305,7 +305,9 @@ class LightGBMClassificationModel(LightGBMModelBase):
 
 class LightGBMRegressionModel(LightGBMModelBase):
     def transform(self, features):
-        return dict(prediction=self.predict_raw(features))
+        # LightGBMRegressionModel.predict: score(features, raw = false): the objective's output transform applies (exp for
+        # poisson / gamma / tweedie, identity otherwise)
+        return dict(prediction=self._native().predict_for_mat(features, LightGBMBooster.PREDICT_NORMAL))
 
 
 class LightGBMRankerModel(LightGBMModelBase):

@@ -1,0 +1,96 @@
+"""Regression objectives beyond L2 (LightGBMRegressor's `objective`, `alpha`, `tweedieVariancePower`
+params, RegressorTrainParams.scala:24-29): huber, fair, poisson, gamma, tweedie gradients on the GPU against the oracle's
+restatement of upstream's regression_objective.hpp; the log-link objectives predict exp(raw score)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from helpers import NativeBooster, NativeDataset, strip_parameters
+from synapseml_b200.data import synthetic as S
+from synapseml_b200.lightgbm.estimators import LightGBMRegressor, LocalDataFrame
+from synapseml_b200.lightgbm.model_text import TextModel
+from synapseml_b200.lightgbm.native import lightgbmlib, validate
+from test_gpu_predict import predict
+from test_gpu_train import FLOAT_RTOL, train_both
+
+pytestmark = pytest.mark.gpu
+
+OBJECTIVES = {
+    "huber": "objective=huber alpha=0.7",
+    "fair": "objective=fair fair_c=2.0",
+    "poisson": "objective=poisson",
+    "gamma": "objective=gamma",
+    "tweedie": "objective=tweedie tweedie_variance_power=1.3",
+}
+
+
+def count_data(n, positive):
+    X, _ = S.dense100(n, f=12)
+    rng = np.random.Generator(np.random.PCG64(11))
+    mu = np.exp(0.4 * X[:, 0] - 0.3 * X[:, 1] + 0.2 * X[:, 2] * X[:, 3])
+    y = rng.poisson(mu).astype(np.float32)
+    if positive:
+        y = (y + rng.uniform(0.1, 1.0, n)).astype(np.float32)
+    return X, y
+
+
+@pytest.mark.parametrize("name", sorted(OBJECTIVES))
+def test_quantized_models_are_byte_identical(native, oracle, name):
+    X, y = count_data(30000, positive=(name == "gamma"))
+    params = OBJECTIVES[name] + " num_leaves=31 max_bin=63 learning_rate=0.1 use_quantized_grad=true stochastic_rounding=false verbosity=-1"
+    nd, nb, ob = train_both(oracle, X, y, params, 10)
+    ms = nb.model()
+    assert strip_parameters(ms) == strip_parameters(ob.save_model_to_string())
+    assert np.array_equal(nb.scores(), ob.scores())
+    assert ("objective=%s\n" % name) in ms
+    raw, normal = predict(nb.handle, X[:2000], 1), predict(nb.handle, X[:2000], 0)
+    assert np.array_equal(raw, TextModel(ms).predict_raw(X[:2000]))
+    if name in ("poisson", "gamma", "tweedie"):
+        assert np.allclose(normal, np.exp(raw), rtol=1e-13, atol=0)
+    else:
+        assert np.array_equal(normal, raw)
+    nb.free()
+    nd.free()
+
+
+def test_float_mode_poisson_with_weights(native, oracle):
+    X, y = count_data(40000, positive=False)
+    w = np.random.Generator(np.random.PCG64(4)).uniform(0.5, 2.0, len(y)).astype(np.float32)
+    params = "objective=poisson num_leaves=31 max_bin=255 verbosity=-1"
+    nd, nb, ob = train_both(oracle, X, y, params, 8, weight=w)
+    sn, so = TextModel(nb.model()).structure(), TextModel(ob.save_model_to_string()).structure()
+    assert sn[:3] == so[:3]
+    a, b = nb.scores(), ob.scores()
+    assert np.abs(a - b).max() <= FLOAT_RTOL * np.abs(b).max()
+    nb.free()
+    nd.free()
+
+
+def test_default_metric_follows_the_objective(native):
+    X, y = count_data(20000, positive=False)
+    params = "objective=poisson num_leaves=15 max_bin=63 verbosity=-1"
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    for _ in range(5):
+        nb.update()
+    lib = lightgbmlib()
+    n = C.c_int()
+    out = np.zeros(4)
+    validate(lib.LGBM_BoosterGetEval(nb.handle, 0, C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+    pred = np.maximum(np.exp(nb.scores()), 1e-10)
+    assert n.value == 1 and np.isclose(out[0], np.mean(pred - y * np.log(pred)), rtol=1e-10)
+    with pytest.raises(Exception):
+        NativeBooster(NativeDataset(X, -y - 1, params), params)          # negative labels are refused
+    nb.free()
+    nd.free()
+
+
+def test_regressor_estimator_with_tweedie(native):
+    X, y = count_data(30000, positive=False)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    model = LightGBMRegressor(objective="tweedie", tweedieVariancePower=1.2, numIterations=30, numLeaves=15).fit(df)
+    assert "objective=tweedie" in model.getNativeModel() and "[tweedie_variance_power: 1.2]" in model.getNativeModel()
+    pred = model.transform(X)["prediction"]
+    assert (pred > 0).all()                                           # exp link
+    assert np.corrcoef(pred, y)[0, 1] > 0.5 and abs(pred.mean() - y.mean()) < 0.05 * y.mean()
