@@ -565,12 +565,12 @@ __global__ void __launch_bounds__(kPartThreads, 6) k_bt_partition(const uint8_t*
 //   P4  per-leaf arrays are written back and the next batch is chosen.
 struct SelectSmem {
   double *gain, *cgain0, *cgain1, *lvalue, *lweight, *p_lo, *p_ro, *p_lw, *p_rw;
-  int *feat, *node, *rank, *cfeat0, *cfeat1, *cnode0, *cnode1, *lparent, *ldepth, *lcount, *c_leaf, *c_node, *p_lc, *p_rc, *p_feature,
+  int *feat, *node, *rank, *order, *cfeat0, *cfeat1, *cnode0, *cnode1, *lparent, *ldepth, *lcount, *c_leaf, *c_node, *p_lc, *p_rc, *p_feature,
       *p_threshold, *p_flags;
   float* p_gain;
   unsigned char *exp, *isleft;
 };
-constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 17 * sizeof(int) + sizeof(float) + 2;
+constexpr size_t kSelectSmemPerLeaf = 9 * sizeof(double) + 18 * sizeof(int) + sizeof(float) + 2;
 __host__ __device__ inline size_t SelectSmemBytes(int L) { return kSelectSmemPerLeaf * static_cast<size_t>((L + 7) & ~7) + 64; }
 
 // The body: one 256-thread sub-block, synchronised with its named barrier.
@@ -580,6 +580,23 @@ __host__ __device__ inline size_t SelectSmemBytes(int L) { return kSelectSmemPer
 //   P2  thread j writes the order-independent tree fields of commit j (from shared memory);
 //   P3  thread 0 applies the order-dependent bookkeeping of Tree::Split (parent/child links, depths, leaf values) in commit order;
 //   P4  per-leaf arrays are written back and the next batch is chosen.
+// S.rank[i] = how many of the nl current leaves come before leaf i in the sequential learner's order (gain descending, real feature
+// ascending, slot ascending): all pairs, shared out over the sub-block's 256 threads.
+__device__ __forceinline__ void SelectRanks(const SelectSmem& S, int nl, int tid, int sub) {
+  for (int i = tid; i < nl; i += kFindThreads) S.rank[i] = 0;
+  SubSync(sub);
+  for (int i = tid & 31; i < nl; i += 32) {
+    const double g = S.gain[i]; const int rf = S.feat[i];
+    int cnt = 0;
+    for (int j = tid >> 5; j < nl; j += kFindThreads / 32) {
+      const double gj = S.gain[j]; const int fj = S.feat[j];
+      cnt += (j != i) && (SplitBetter(gj, fj, g, rf) || (!SplitBetter(g, rf, gj, fj) && j < i));
+    }
+    if (cnt) atomicAdd(&S.rank[i], cnt);
+  }
+  SubSync(sub);
+}
+
 __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl* ctrl, const TreeArraysDev& T,
                                            const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P, int max_nodes,
                                            int spec_budget, int max_batch, double* sel_smem_raw, int sub) {
@@ -592,7 +609,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     S.gain = d; d += Lc; S.cgain0 = d; d += Lc; S.cgain1 = d; d += Lc; S.lvalue = d; d += Lc; S.lweight = d; d += Lc;
     S.p_lo = d; d += Lc; S.p_ro = d; d += Lc; S.p_lw = d; d += Lc; S.p_rw = d; d += Lc;
     int* q = reinterpret_cast<int*>(d);
-    S.feat = q; q += Lc; S.node = q; q += Lc; S.rank = q; q += Lc; S.cfeat0 = q; q += Lc; S.cfeat1 = q; q += Lc;
+    S.feat = q; q += Lc; S.node = q; q += Lc; S.rank = q; q += Lc; S.order = q; q += Lc; S.cfeat0 = q; q += Lc; S.cfeat1 = q; q += Lc;
     S.cnode0 = q; q += Lc; S.cnode1 = q; q += Lc; S.lparent = q; q += Lc; S.ldepth = q; q += Lc; S.lcount = q; q += Lc;
     S.c_leaf = q; q += Lc; S.c_node = q; q += Lc; S.p_lc = q; q += Lc; S.p_rc = q; q += Lc; S.p_feature = q; q += Lc;
     S.p_threshold = q; q += Lc; S.p_flags = q; q += Lc;
@@ -600,7 +617,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     unsigned char* c = reinterpret_cast<unsigned char*>(q);
     S.exp = c; c += Lc; S.isleft = c;
   }
-  const int tid = threadIdx.x & (kFindThreads - 1), lane = tid & 31;
+  const int tid = threadIdx.x & (kFindThreads - 1);
   const int nl0 = ctrl->num_leaves;
   // ---- P0
   for (int i = tid; i < nl0; i += kFindThreads) {
@@ -627,39 +644,44 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     S.isleft[i] = par >= 0 ? (T.left_child[par] == ~i) : 0;
   }
   SubSync(sub);
-  // ---- P1: replay the sequential order as far as the already expanded leaves allow (warp 0)
-  if (tid < 32) {
+  LGB_TRACE(ctrl, 43);
+  // ---- P1: replay the sequential order as far as the already expanded leaves allow.  Children of a committed leaf are never
+  //      expanded yet, so the replay commits the initial leaves in rank order until the best entry is not an expanded initial
+  //      leaf: rank them once (all threads), then one thread walks the ranks against the best child inserted so far.
+  SelectRanks(S, nl0, tid, sub);
+  for (int i = tid; i < nl0; i += kFindThreads) S.order[S.rank[i]] = i;
+  SubSync(sub);
+  if (tid == 0) {
     int nl = nl0, m = 0, state = 0;
+    double cg = KMINSCORE; int cf = -1, cs = -1;      // best child so far: gain, real feature, slot
     while (true) {
-      double bg = KMINSCORE; int bf = -1, bi = -1;
-      for (int i = lane; i < nl; i += 32) {
-        const double g = S.gain[i]; const int rf = S.feat[i];
-        if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = i; }        // ascending i: the earlier leaf keeps ties
-      }
-      for (int o = 16; o > 0; o >>= 1) {
-        const double g = __shfl_xor_sync(0xffffffffu, bg, o);
-        const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
-        const int i = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf) || (!SplitBetter(bg, bf, g, rf) && i < bi))) { bg = g; bf = rf; bi = i; }
+      const int s = m < nl0 ? S.order[m] : -1;       // the m-th best initial leaf (every earlier one was committed)
+      bool leaf_best = s >= 0;
+      double bg = KMINSCORE;
+      if (s >= 0) {
+        const double g = S.gain[s]; const int rf = S.feat[s];
+        bg = g;
+        if (cs >= 0 && (SplitBetter(cg, cf, g, rf) || (!SplitBetter(g, rf, cg, cf) && cs < s))) { leaf_best = false; bg = cg; }
+      } else {
+        bg = cg;
       }
       if (nl >= L || !(bg > 0.0)) { state = 1; break; }
-      if (!S.exp[bi]) { state = 2; break; }
+      if (!leaf_best || !S.exp[s]) { state = 2; break; }
       // commit: the left child keeps the leaf id, the right child becomes leaf `nl`
-      __syncwarp();
-      if (lane == 0) {
-        S.c_leaf[m] = bi; S.c_node[m] = S.node[bi];
-        const int l = S.cnode0[bi], r = S.cnode1[bi];
-        const double gl = S.cgain0[bi], gr = S.cgain1[bi];
-        const int fl = S.cfeat0[bi], fr = S.cfeat1[bi];
-        S.node[bi] = l; S.gain[bi] = gl; S.feat[bi] = fl; S.exp[bi] = 0;
-        S.node[nl] = r; S.gain[nl] = gr; S.feat[nl] = fr; S.exp[nl] = 0;
-      }
+      S.c_leaf[m] = s; S.c_node[m] = S.node[s];
+      const int l = S.cnode0[s], r = S.cnode1[s];
+      const double gl = S.cgain0[s], gr = S.cgain1[s];
+      const int fl = S.cfeat0[s], fr = S.cfeat1[s];
+      S.node[s] = l; S.gain[s] = gl; S.feat[s] = fl; S.exp[s] = 0;
+      S.node[nl] = r; S.gain[nl] = gr; S.feat[nl] = fr; S.exp[nl] = 0;
+      if (cs < 0 || SplitBetter(gl, fl, cg, cf) || (!SplitBetter(cg, cf, gl, fl) && s < cs)) { cg = gl; cf = fl; cs = s; }
+      if (SplitBetter(gr, fr, cg, cf) || (!SplitBetter(cg, cf, gr, fr) && nl < cs)) { cg = gr; cf = fr; cs = nl; }
       ++nl; ++m;
-      __syncwarp();
     }
-    if (lane == 0) { s_state = state; s_nl = nl; s_m = m; }
+    s_state = state; s_nl = nl; s_m = m;
   }
   SubSync(sub);
+  LGB_TRACE(ctrl, 44);
   const int nl = s_nl, m = s_m;
   // ---- P2: order-independent fields of every commit (a leaf id commits at most once per replay, so the commit data loaded
   //      for it in P0 is still the committed node's)
@@ -694,6 +716,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     }
   }
   SubSync(sub);
+  LGB_TRACE(ctrl, 45);
   // ---- P4: write the per-leaf arrays back
   if (m > 0) {
     for (int i = tid; i < nl; i += kFindThreads) {
@@ -708,18 +731,9 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   }
   // ---- next batch: the best not-yet-expanded leaves whose rank is below the remaining leaf budget
   const int budget = L - nl;
-  for (int i = tid; i < nl; i += kFindThreads) {
-    const double g = S.gain[i]; const int rf = S.feat[i];
-    int rank = 0;
-    for (int j = 0; j < nl; ++j) {
-      if (j == i) continue;
-      const double gj = S.gain[j]; const int fj = S.feat[j];
-      rank += SplitBetter(gj, fj, g, rf) || (!SplitBetter(g, rf, gj, fj) && j < i);
-    }
-    S.rank[i] = rank;
-  }
   if (tid == 0) s_count = 0;
-  SubSync(sub);
+  SelectRanks(S, nl, tid, sub);
+  LGB_TRACE(ctrl, 46);
   // expansions that are not committed yet (the batch's first leaf is certain to be committed by the next replay, the others
   // are speculative): bounding them bounds the nodes / pool slots a tree can consume to (L - 1) + spec_budget expansions
   const int num_nodes = ctrl->num_nodes, num_slots = ctrl->num_slots;
@@ -755,6 +769,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     }
   }
   SubSync(sub);
+  LGB_TRACE(ctrl, 47);
   if (tid == 0) {
     const int bn = s_count;
     ctrl->batch_n = bn;
