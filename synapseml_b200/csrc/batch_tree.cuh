@@ -731,7 +731,6 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   }
   // ---- next batch: the best not-yet-expanded leaves whose rank is below the remaining leaf budget
   const int budget = L - nl;
-  if (tid == 0) s_count = 0;
   SelectRanks(S, nl, tid, sub);
   LGB_TRACE(ctrl, 46);
   // expansions that are not committed yet (the batch's first leaf is certain to be committed by the next replay, the others
@@ -742,14 +741,19 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   const int node_room = (max_nodes - num_nodes) / 2;
   int kmax = min(min(max_batch, 1 + spec_left), node_room);
   if (kmax < 1) kmax = 1;
-  for (int i = tid; i < nl; i += kFindThreads) {
-    const bool eligible = !S.exp[i] && S.gain[i] > 0.0 && S.rank[i] < budget;
-    if (!eligible) continue;
-    int pos = 0;
-    for (int j = 0; j < nl; ++j)
-      if (j != i && !S.exp[j] && S.gain[j] > 0.0 && S.rank[j] < budget && S.rank[j] < S.rank[i]) ++pos;
-    if (pos < kmax) {
-      atomicAdd(&s_count, 1);
+  // the first kmax eligible leaves in rank order: warp 0 walks the ranks 32 at a time, a ballot gives every eligible leaf its place
+  for (int i = tid; i < nl; i += kFindThreads) S.order[S.rank[i]] = i;
+  SubSync(sub);
+  const int rlim = min(nl, budget);
+  int taken = 0;
+  for (int r0 = 0; tid < 32 && r0 < rlim && taken < kmax; r0 += 32) {
+    const int r = r0 + tid;
+    const int i = r < rlim ? S.order[r] : -1;
+    const bool eligible = i >= 0 && !S.exp[i] && S.gain[i] > 0.0;
+    const unsigned emask = __ballot_sync(0xffffffffu, eligible);
+    const int pos = taken + __popc(emask & ((1u << tid) - 1u));
+    taken += __popc(emask);
+    if (eligible && pos < kmax) {
       const int nd = S.node[i];
       const NodeDev& par = nodes[nd];
       const SplitDev& bs = par.best;
@@ -768,6 +772,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       ctrl->batch[pos] = it;
     }
   }
+  if (tid == 0) s_count = min(taken, kmax);
   SubSync(sub);
   LGB_TRACE(ctrl, 47);
   if (tid == 0) {
