@@ -356,6 +356,23 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
                          fb + f, spl, &tg, &th, sub);
     if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
   }
+  if (P.reduce_in_select) {
+    // the replay kernel picks the child's best feature (SelectReduceChildren); the first unit publishes everything else
+    if (f == 0 && b == 0) {
+      if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
+        me.int_g = tg; me.int_h = th;
+        me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
+      }
+      NodeDev& N = nodes[node];
+      N.begin = me.begin; N.count = me.count; N.buf = me.buf; N.global_count = me.global_count;
+      N.int_g = me.int_g; N.int_h = me.int_h; N.sum_g = me.sum_g; N.sum_h = me.sum_h;
+      N.depth = me.depth; N.hist_slot = me.hist_slot; N.state = me.state; N.left = me.left; N.right = me.right; N.pad_ = 0;
+      N.child_feat[0] = N.child_feat[1] = -1; N.child_count[0] = N.child_count[1] = 0;
+      N.child_gain[0] = N.child_gain[1] = KMINSCORE;
+    }
+    SubSync(sub);
+    return;
+  }
   __threadfence();
   SubSync(sub);
   if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == F - 1);
@@ -597,9 +614,52 @@ __device__ __forceinline__ void SelectRanks(const SelectSmem& S, int nl, int tid
   SubSync(sub);
 }
 
+// LearnerParams::reduce_in_select: one warp per child of the round that was searched — its best feature out of the per-feature
+// results the split search left in feat_best (ties: the lower real feature, as the search's own reduction), copied into the
+// child's node record, and the child's summary into its parent's.
+__device__ __forceinline__ void SelectReduceChildren(NodeDev* nodes, const BatchCtrl* ctrl, const SplitDev* feat_best,
+                                                     const LearnerParams& P, int after_root, int tid) {
+  const int F = P.num_features;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int units = after_root ? 1 : 2 * ctrl->batch_n;
+  for (int kc = warp; kc < units; kc += kFindThreads / 32) {
+    const int k = kc >> 1, c = kc & 1;
+    int node = 0, parent = -1, side = 0, count = 0;
+    if (!after_root) {
+      const BatchItem& it = ctrl->batch[k];
+      const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
+      if (!g.find) continue;         // published by the split search itself (no candidates)
+      const bool is_left = (c == 0) == g.left_smaller;
+      node = is_left ? it.left : it.right;
+      side = is_left ? 0 : 1;
+      parent = it.node;
+      count = is_left ? g.lc : g.rc;
+    }
+    const SplitDev* fb = feat_best + static_cast<size_t>(kc) * F;
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int j = lane; j < F; j += 32) {
+      const double g = fb[j].gain; const int rf = fb[j].real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
+    }
+    const int* src = reinterpret_cast<const int*>(fb + bi);
+    int* dst = reinterpret_cast<int*>(&nodes[node].best);
+    for (int w = lane; w < static_cast<int>(sizeof(SplitDev) / sizeof(int)); w += 32) dst[w] = src[w];
+    if (lane == 0 && parent >= 0) {
+      nodes[parent].child_gain[side] = bg; nodes[parent].child_feat[side] = bf; nodes[parent].child_count[side] = count;
+    }
+  }
+}
+
 __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl* ctrl, const TreeArraysDev& T,
                                            const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P, int max_nodes,
-                                           int spec_budget, int max_batch, double* sel_smem_raw, int sub) {
+                                           int spec_budget, int max_batch, double* sel_smem_raw, int sub,
+                                           const SplitDev* feat_best, int after_root) {
   __shared__ int s_state, s_nl, s_m, s_count;
   const int L = P.num_leaves;
   const int Lc = (L + 7) & ~7;
@@ -619,6 +679,10 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   }
   const int tid = threadIdx.x & (kFindThreads - 1);
   const int nl0 = ctrl->num_leaves;
+  if (P.reduce_in_select) {
+    SelectReduceChildren(nodes, ctrl, feat_best, P, after_root, tid);
+    SubSync(sub);      // P0 reads the node records just completed (same CTA: the barrier orders them)
+  }
   // ---- P0
   for (int i = tid; i < nl0; i += kFindThreads) {
     const int nd = avail[i];
@@ -790,14 +854,15 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
 
 __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, int* __restrict__ avail, BatchCtrl* __restrict__ ctrl,
                                                    TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
-                                                   int max_nodes, int spec_budget, int max_batch) {
+                                                   int max_nodes, int spec_budget, int max_batch, const SplitDev* feat_best,
+                                                   int after_root) {
   PdlLaunchDependents();
   LGB_TRACE(ctrl, 40);
   PdlWait();
   LGB_TRACE(ctrl, 41);
   if (ctrl->done) return;
   extern __shared__ double sel_smem_raw[];
-  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw, 0);
+  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw, 0, feat_best, after_root);
   LGB_TRACE(ctrl, 42);
 }
 

@@ -105,6 +105,9 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   lp_.num_grad_quant_bins = cfg_.num_grad_quant_bins; lp_.stochastic_rounding = cfg_.stochastic_rounding;
   lp_.const_hessian = (obj_ == kL2 && !has_weights_);
   lp_.seed = static_cast<unsigned int>(cfg_.seed);
+  // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
+  // search's last unit does, as for wide data)
+  lp_.reduce_in_select = F_ <= 32 && !(getenv("LGB_B200_REDUCE_IN_SELECT") && atoi(getenv("LGB_B200_REDUCE_IN_SELECT")) == 0);
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -522,10 +525,10 @@ void Booster::LaunchFind(bool root) {
 
 // Replay + next batch.  (Running it inside the split-search kernel's last sub-block was measured: no faster — the replay's own
 // ~10 us stay on the critical path and the search kernel loses registers.)
-void Booster::LaunchSelect() {
+void Booster::LaunchSelect(bool after_root) {
   ProfBegin("select");
   LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p,
-            lp_, max_nodes_, spec_budget_, max_batch_);
+            lp_, max_nodes_, spec_budget_, max_batch_, static_cast<const SplitDev*>(d_feat_best_.p), after_root ? 1 : 0);
   ProfEnd();
   ++launches_;
 }
@@ -585,7 +588,7 @@ void Booster::EnqueueRounds(int rounds) {
     ProfEnd();
     ProfBegin("hist"); LaunchHist(false); ProfEnd();
     ProfBegin("find"); LaunchFind(false); ProfEnd();
-    LaunchSelect();
+    LaunchSelect(false);
     launches_ += 1;
   }
 }
@@ -645,7 +648,7 @@ void Booster::TrainTree(HostTree* out) {
   }
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
-  LaunchSelect();
+  LaunchSelect(true);
   // the number of rounds a tree needs is only known on the device: enqueue as many as the previous tree used (+1), then look
   int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + 1) : std::min(L - 1, (L - 1) / 2 + 2);
   int total = 0;

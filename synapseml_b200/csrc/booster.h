@@ -73,6 +73,8 @@ struct LearnerParams {
   int min_data_in_leaf, max_depth, num_leaves, num_features;
   int quantized, dp, num_grad_quant_bins, stochastic_rounding, const_hessian;
   unsigned int seed;
+  int reduce_in_select;                   // few features: the replay kernel reduces the per-feature results of a child (no last-arriver
+                                          // reduction at the end of the split search)
   const unsigned char* feature_mask;      // [F] 1 = this tree may split on the feature (feature_fraction < 1), nullptr = all
 };
 
@@ -252,7 +254,7 @@ class Booster {
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
   void LaunchTreeKernel();
-  void LaunchSelect();
+  void LaunchSelect(bool after_root);
   void DumpTrace();
   bool FetchTree(HostTree* out);
   void UpdateScores();

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_bt_tree(const TreeKernelArg
   TreeFindPhase<!FLT>(a, true, s_list);
   grid.sync();
   if (blockIdx.x == 0 && threadIdx.x < kFindThreads)
-    SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0);
+    SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0, a.feat_best, 1);
   grid.sync();
   // ---- rounds
   while (!ctrl->done) {
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_bt_tree(const TreeKernelArg
     TreeFindPhase<!FLT>(a, false, s_list);
     grid.sync();
     if (blockIdx.x == 0 && threadIdx.x < kFindThreads)
-      SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0);
+      SelectBody(a.nodes, a.avail, ctrl, a.T, a.fmeta, a.P, a.max_nodes, a.spec_budget, a.max_batch, sel_smem, 0, a.feat_best, 0);
     grid.sync();
   }
 }
