@@ -635,21 +635,18 @@ __device__ __forceinline__ void SelectReduceChildren(NodeDev* nodes, const Batch
       parent = it.node;
       count = is_left ? g.lc : g.rc;
     }
+    // lane j holds feature j's whole result (F <= 32), so the winner stores it without a second trip to memory
     const SplitDev* fb = feat_best + static_cast<size_t>(kc) * F;
+    SplitDev mine;
     double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int j = lane; j < F; j += 32) {
-      const double g = fb[j].gain; const int rf = fb[j].real_feature;
-      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
-    }
+    if (lane < F) { mine = fb[lane]; bg = mine.gain; bf = mine.real_feature; bi = lane; }
     for (int o = 16; o > 0; o >>= 1) {
       const double g = __shfl_xor_sync(0xffffffffu, bg, o);
       const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
       const int i = __shfl_xor_sync(0xffffffffu, bi, o);
       if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
     }
-    const int* src = reinterpret_cast<const int*>(fb + bi);
-    int* dst = reinterpret_cast<int*>(&nodes[node].best);
-    for (int w = lane; w < static_cast<int>(sizeof(SplitDev) / sizeof(int)); w += 32) dst[w] = src[w];
+    if (lane == bi) nodes[node].best = mine;
     if (lane == 0 && parent >= 0) {
       nodes[parent].child_gain[side] = bg; nodes[parent].child_feat[side] = bf; nodes[parent].child_count[side] = count;
     }
@@ -679,13 +676,22 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
   }
   const int tid = threadIdx.x & (kFindThreads - 1);
   const int nl0 = ctrl->num_leaves;
+  // the first leaf of every thread: what does not depend on this round's split search is requested before the reduction below,
+  // so those round trips overlap it
+  int pre_nd = 0, pre_par = -1, pre_depth = 0, pre_count = 0;
+  double pre_value = 0.0, pre_weight = 0.0;
+  if (tid < nl0) {
+    pre_nd = avail[tid]; pre_par = T.leaf_parent[tid]; pre_depth = T.leaf_depth[tid]; pre_value = T.leaf_value[tid];
+    pre_weight = T.leaf_weight[tid]; pre_count = T.leaf_count[tid];
+  }
   if (P.reduce_in_select) {
     SelectReduceChildren(nodes, ctrl, feat_best, P, after_root, tid);
     SubSync(sub);      // P0 reads the node records just completed (same CTA: the barrier orders them)
   }
   // ---- P0
   for (int i = tid; i < nl0; i += kFindThreads) {
-    const int nd = avail[i];
+    const bool first = i == tid;
+    const int nd = first ? pre_nd : avail[i];
     const NodeDev& N = nodes[nd];
     S.node[i] = nd; S.gain[i] = N.best.gain; S.feat[i] = N.best.real_feature;
     const bool e = N.state == 1;
@@ -702,9 +708,10 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       S.p_flags[i] = (N.best.default_left ? 2 : 0) | ((N.best.missing_type & 3) << 2);      // = Tree's decision_type
       S.p_gain[i] = static_cast<float>(N.best.gain);
     }
-    const int par = T.leaf_parent[i];
-    S.lparent[i] = par; S.ldepth[i] = T.leaf_depth[i]; S.lvalue[i] = T.leaf_value[i]; S.lweight[i] = T.leaf_weight[i];
-    S.lcount[i] = T.leaf_count[i];
+    const int par = first ? pre_par : T.leaf_parent[i];
+    S.lparent[i] = par; S.ldepth[i] = first ? pre_depth : T.leaf_depth[i]; S.lvalue[i] = first ? pre_value : T.leaf_value[i];
+    S.lweight[i] = first ? pre_weight : T.leaf_weight[i];
+    S.lcount[i] = first ? pre_count : T.leaf_count[i];
     S.isleft[i] = par >= 0 ? (T.left_child[par] == ~i) : 0;
   }
   SubSync(sub);
