@@ -131,6 +131,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   }
   if (const char* env = getenv("LGB_B200_PART_BLOCKS")) part_blocks_ = std::max(1, atoi(env));
   spec_budget_ = std::max(2 * kMaxBatch, (L - 1) / 2);
+  if (const char* env = getenv("LGB_B200_SPEC_BUDGET")) spec_budget_ = std::max(0, atoi(env));      // experiments
   const int max_expansions = (L - 1) + spec_budget_;
   max_nodes_ = 1 + 2 * max_expansions;
   const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
