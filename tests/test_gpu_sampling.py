@@ -19,14 +19,16 @@ CASES = {
     "bagging": "objective=binary num_leaves=31 max_bin=63 bagging_fraction=0.7 bagging_freq=1",
     "bagging_every_third": "objective=binary num_leaves=31 max_bin=255 bagging_fraction=0.4 bagging_freq=3 bagging_seed=9",
     "both_l2": "objective=regression num_leaves=31 max_bin=63 bagging_fraction=0.8 bagging_freq=2 feature_fraction=0.7",
+    # more than 32 features: the split search's own last-unit reduction instead of the replay kernel's
+    "both_l2_wide": "objective=regression num_leaves=31 max_bin=63 bagging_fraction=0.8 bagging_freq=1 feature_fraction=0.5",
 }
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_quantized_models_with_sampling_are_byte_identical(native, oracle, case):
     params = CASES[case] + QUANT
-    if case == "both_l2":
-        X, y = S.dense100(40000, f=20)
+    if case.startswith("both_l2"):
+        X, y = S.dense100(40000, f=48 if case.endswith("wide") else 20)
     else:
         X, y = S.higgs_shape(50000 + 317)         # a ragged last 1024-row bagging block
     nd, nb, ob = train_both(oracle, X, y, params, 10)
