@@ -88,10 +88,8 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       if (ROOT) {
         row = begin + p;
         if (FLT) { const int2 t = ghfix[row]; gx = static_cast<unsigned>(t.x); hx = static_cast<unsigned>(t.y); }
-        else {
-          const unsigned w = gh16[row];
-          pk = (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
-        }
+        else pk = gh16[row];      // raw (int8 g << 8 | int8 h): unpacked by unpack() where it is consumed, not here — the unpacking
+                                  // instructions would wait for the load at the point of issue and stall the whole pipeline
       } else if (FLT) {
         const int4 e = reinterpret_cast<const int4*>(idx)[begin + p];
         row = e.x; gx = static_cast<unsigned>(e.y); hx = static_cast<unsigned>(e.z);
@@ -99,6 +97,10 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
         const int2 e = reinterpret_cast<const int2*>(idx)[begin + p];
         row = e.x; pk = static_cast<unsigned>(e.y);
       }
+    };
+    auto unpack = [](unsigned w) -> unsigned {      // -> (g << 16) + h, the shared-memory update word
+      if (ROOT && !FLT) return (static_cast<unsigned>(static_cast<int>(static_cast<signed char>(w >> 8))) << 16) + (w & 0xffu);
+      return w;
     };
     auto load_bins = [&](int row_l, int p0, int unit, unsigned (&bb)[U]) {
       if (ROOT) {
@@ -125,6 +127,7 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       unsigned pk_cur = 0, gx_cur = 0, hx_cur = 0, pk_nxt = 0, gx_nxt = 0, hx_nxt = 0;
       load_entry(first + lane, row_cur, pk_cur, gx_cur, hx_cur);
       if (ng > 1) load_entry(first + gstride + lane, row_nxt, pk_nxt, gx_nxt, hx_nxt);
+      pk_cur = unpack(pk_cur);
       unsigned b_cur[U];
       load_bins(row_cur, first, 0, b_cur);
       #pragma unroll 1
@@ -156,7 +159,7 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
           for (int u = 0; u < U; ++u) b_cur[u] = b_nxt[u];
         }
         row_cur = row_nxt; row_nxt = row_nn;
-        pk_cur = pk_nxt; gx_cur = gx_nxt; hx_cur = hx_nxt;
+        pk_cur = unpack(pk_nxt); gx_cur = gx_nxt; hx_cur = hx_nxt;      // loaded one group ago
         pk_nxt = pk_nn; gx_nxt = gx_nn; hx_nxt = hx_nn;
       }
     }
@@ -167,7 +170,7 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       const bool v = p < sub_hi;
       int row_l = -1;
       unsigned pk_l = 0, gx_l = 0, hx_l = 0;
-      if (v) load_entry(p, row_l, pk_l, gx_l, hx_l);
+      if (v) { load_entry(p, row_l, pk_l, gx_l, hx_l); pk_l = unpack(pk_l); }
       #pragma unroll 1
       for (int s = 0; s < STEPS; ++s) {
         const int srcl = s * R + r;
