@@ -1,4 +1,4 @@
-"""Scratch GPU check used during bring-up (not collected by pytest)."""
+"""Scratch GPU check used during bring-up (run by hand: python experiments/quick_gpu.py)."""
 import ctypes as C, sys, time, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
