@@ -1,8 +1,7 @@
 """Reader for the LightGBM text model with a vectorised numpy predictor.
 
-Used by the model classes' transform() (the reference scores rows through LGBM_BoosterPredictForMatSingle,
-booster/LightGBMBooster.scala:520-557 — native single-row predict is a later row of the scope table) and by the tests to
-compare models produced by the CUDA library and by the oracle.
+Used by the model classes for feature importances and by the tests, as an independent traversal, to compare models and scores
+produced by the CUDA library and by the oracle.  (Scoring itself goes through the library: LGBM_BoosterPredictForMat on the GPU.)
 """
 import numpy as np
 
