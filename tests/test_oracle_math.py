@@ -77,3 +77,45 @@ def test_quantized_integer_gradients(oracle):
     exp_h = np.trunc(h.astype(np.float64) * (1.0 / sc[1]) + 0.5).astype(np.int8)
     assert np.array_equal(qg, exp_g) and np.array_equal(qh, exp_h)
     assert qg.min() >= -2 and qg.max() <= 2 and qh.min() >= 0 and qh.max() <= 4
+
+
+def test_regression_objective_gradients_closed_form(oracle):
+    """First-iteration gradients of huber / fair / poisson / gamma / tweedie against the formulas of upstream's
+    regression_objective.hpp written out in numpy (scores = the automatic initial score: mean label, or its log for the log-link
+    objectives).  float32 results may differ by one ulp where numpy's exp and the software exp differ in the last bit."""
+    rng = np.random.Generator(np.random.PCG64(3))
+    n = 400
+    X = rng.normal(size=(n, 2))
+    y = rng.poisson(np.exp(0.5 * X[:, 0])).astype(np.float32) + np.float32(0.25)
+    w = rng.uniform(0.5, 2.0, n).astype(np.float32)
+    mean = float(np.sum(y.astype(np.float64)) / n)
+
+    def check(objective, extra, s0, gfun):
+        params = "objective=%s %s min_data_in_leaf=1 num_leaves=2 verbosity=-1" % (objective, extra)
+        bst, _ = oracle.fit(X, y, params, num_iterations=1)
+        g, h = bst.gradients()
+        eg, eh = gfun(np.full(n, s0), y.astype(np.float64))
+        assert np.allclose(g, eg.astype(np.float32), rtol=2e-7, atol=0), objective
+        assert np.allclose(h, eh.astype(np.float32), rtol=2e-7, atol=0), objective
+        assert ("objective=%s\n" % objective) in bst.save_model_to_string()
+
+    a = 0.7
+    check("huber", "alpha=%g" % a, mean,
+          lambda s, t: (np.where(np.abs(s - t) <= a, s - t, np.sign(s - t) * a), np.ones(n)))
+    c = 2.0
+    check("fair", "fair_c=%g" % c, mean,
+          lambda s, t: (c * (s - t) / (np.abs(s - t) + c), c * c / (np.abs(s - t) + c) ** 2))
+    check("poisson", "", np.log(mean),
+          lambda s, t: (np.exp(s) - t, np.exp(s) * np.exp(0.7)))
+    check("gamma", "", np.log(mean),
+          lambda s, t: (1.0 - t * np.exp(-s), t * np.exp(-s)))
+    rho = 1.3
+    check("tweedie", "tweedie_variance_power=%g" % rho, np.log(mean),
+          lambda s, t: (-t * np.exp((1 - rho) * s) + np.exp((2 - rho) * s),
+                        -t * (1 - rho) * np.exp((1 - rho) * s) + (2 - rho) * np.exp((2 - rho) * s)))
+    # weights multiply both
+    bst, _ = oracle.fit(X, y, "objective=poisson min_data_in_leaf=1 num_leaves=2 verbosity=-1", num_iterations=1, weight=w)
+    g, h = bst.gradients()
+    s0 = np.log(np.sum(y.astype(np.float64) * w) / np.sum(w.astype(np.float64)))
+    assert np.allclose(g, ((np.exp(s0) - y) * w).astype(np.float32), rtol=3e-7, atol=1e-7)
+    assert np.allclose(h, (np.exp(s0) * np.exp(0.7) * w).astype(np.float32), rtol=3e-7, atol=0)
