@@ -169,6 +169,13 @@ class Booster:
         _check(lib().ORC_BoosterUpdateOneIter(self.h, C.byref(fin)))
         return bool(fin.value)
 
+    def update_one_iter_custom(self, grad, hess):
+        g = np.ascontiguousarray(grad, dtype=np.float32)
+        h = np.ascontiguousarray(hess, dtype=np.float32)
+        fin = C.c_int()
+        _check(lib().ORC_BoosterUpdateOneIterCustom(self.h, _ptr(g, C.c_float), _ptr(h, C.c_float), C.byref(fin)))
+        return bool(fin.value)
+
     def save_model_to_string(self):
         n = C.c_int64()
         buf = C.create_string_buffer(1 << 16)

@@ -122,6 +122,12 @@ int ORC_BoosterUpdateOneIter(void* h, int* is_finished) {
   ORC_END
 }
 
+int ORC_BoosterUpdateOneIterCustom(void* h, const float* grad, const float* hess, int* is_finished) {
+  ORC_BEGIN
+  *is_finished = static_cast<Booster*>(h)->TrainOneIter(grad, hess) ? 1 : 0;
+  ORC_END
+}
+
 int ORC_BoosterSaveModelToString(void* h, int64_t buf_len, int64_t* out_len, char* out) {
   ORC_BEGIN
   std::string s = static_cast<Booster*>(h)->SaveModelToString();

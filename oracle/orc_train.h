@@ -260,8 +260,8 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE } obj = OBJ_L2;
-  bool IsPointRegression() const { return obj == OBJ_L2 || obj >= OBJ_HUBER; }
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM } obj = OBJ_L2;
+  bool IsPointRegression() const { return obj == OBJ_L2 || (obj >= OBJ_HUBER && obj <= OBJ_TWEEDIE); }
   bool LogLink() const { return obj == OBJ_POISSON || obj == OBJ_GAMMA || obj == OBJ_TWEEDIE; }
   bool need_train = true;
   double label_weights[2] = {1.0, 1.0};
@@ -376,6 +376,8 @@ class Booster {
       obj = cfg.objective == "poisson" ? OBJ_POISSON : cfg.objective == "gamma" ? OBJ_GAMMA : OBJ_TWEEDIE;
       for (auto& sh : shards) for (float l : sh.ds->label)      // RegressionPoissonLoss::Init / Gamma: label domain
         if (l < 0.0f || (obj == OBJ_GAMMA && l <= 0.0f)) throw std::runtime_error("oracle: " + cfg.objective + " needs non-negative labels");
+    } else if (cfg.objective == "custom" || cfg.objective == "none") {
+      obj = OBJ_CUSTOM;      // no objective function: gradients come from the caller (TrainOneIter(grad, hess))
     } else if (cfg.objective == "lambdarank") {
       obj = OBJ_LAMBDARANK;
       label_gain = cfg.label_gain;
@@ -491,6 +493,8 @@ class Booster {
             sh.hess[i] = static_cast<score_t>(d->weight[i]);
           }
         }
+      } else if (obj == OBJ_CUSTOM) {
+        throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
       } else if (obj != OBJ_LAMBDARANK) {
         // regression_objective.hpp: Huber (alpha), Fair (fair_c), Poisson (poisson_max_delta_step), Gamma, Tweedie (rho); exp is the
         // software exp shared with the CUDA library
@@ -819,9 +823,13 @@ class Booster {
   }
 
   // ---------------------------------------------------------------- GBDT (A.9)
-  bool TrainOneIter() {
+  // GBDT::TrainOneIter(gradients, hessians): with caller-supplied arrays (one value per row, shard after shard) there is no
+  // automatic initial score and the objective's own gradients are not computed
+  bool TrainOneIter(const float* custom_grad = nullptr, const float* custom_hess = nullptr) {
     double init_score = 0.0;
-    if (models.empty() && !shards[0].ds->has_init_score && cfg.boost_from_average && obj != OBJ_LAMBDARANK) {
+    const bool custom = custom_grad != nullptr;
+    if (obj == OBJ_CUSTOM && !custom) throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
+    if (!custom && models.empty() && !shards[0].ds->has_init_score && cfg.boost_from_average && obj != OBJ_LAMBDARANK) {
       double v = BoostFromScore();
       // ObtainAutomaticInitialScore: GlobalSyncUpByMean over machines (every machine holds the same value)
       if (S > 1) { double acc = 0.0; for (int s = 0; s < S; ++s) acc += v; v = acc / S; }
@@ -830,7 +838,15 @@ class Booster {
         for (auto& sh : shards) for (auto& x : sh.score) x += v;
       }
     }
-    GetGradients();
+    if (custom) {
+      size_t off = 0;
+      for (auto& sh : shards) {
+        for (size_t i = 0; i < sh.grad.size(); ++i) { sh.grad[i] = custom_grad[off + i]; sh.hess[i] = custom_hess[off + i]; }
+        off += sh.grad.size();
+      }
+    } else {
+      GetGradients();
+    }
     Bagging();
     bool should_continue = false;
     std::unique_ptr<Tree> tree(new Tree(2));
@@ -886,6 +902,7 @@ class Booster {
   std::string ObjectiveString() const {
     if (obj == OBJ_BINARY) return "binary sigmoid:" + FmtG(cfg.sigmoid);
     if (obj == OBJ_L2) return "regression";
+    if (obj == OBJ_CUSTOM) return "";
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }
@@ -899,7 +916,7 @@ class Booster {
     s += "num_tree_per_iteration=1\n";
     s += "label_index=0\n";
     s += "max_feature_idx=" + std::to_string(d->num_total_features - 1) + "\n";
-    s += "objective=" + ObjectiveString() + "\n";
+    if (!ObjectiveString().empty()) s += "objective=" + ObjectiveString() + "\n";      // none without an objective function
     s += "feature_names=";
     for (int j = 0; j < d->num_total_features; ++j) { if (j) s += ' '; s += d->feature_names[j]; }
     s += "\nfeature_infos=";

@@ -50,6 +50,28 @@ def test_builtin_gradients_through_the_custom_entry_point_grow_the_same_trees(na
     nd.free()
 
 
+def test_user_gradients_give_the_oracles_model(native, oracle):
+    """Gradients that no built-in objective produces (the reference test's log-likelihood, computed in numpy from the raw scores
+    LGBM_BoosterGetPredict returns) go to the CUDA library and to the oracle alike: quantized models are byte-identical."""
+    from helpers import oracle_dataset, strip_parameters
+    X, y = S.higgs_shape(40000)
+    params = ("objective=custom num_leaves=31 max_bin=63 min_data_in_leaf=20 use_quantized_grad=true stochastic_rounding=false "
+              "bagging_fraction=0.8 bagging_freq=1 verbosity=-1")
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    _, dss, _ = oracle_dataset(oracle, X, y, params)
+    ob = oracle.Booster(dss, params)
+    for _ in range(8):
+        s = nb.scores()
+        assert np.array_equal(s, ob.scores())
+        prob = 1.0 / (1.0 + np.exp(-s))
+        g, h = (prob - y).astype(np.float32), (prob * (1.0 - prob)).astype(np.float32)
+        assert update_custom(nb, g, h) == ob.update_one_iter_custom(g, h)
+    assert strip_parameters(nb.model()) == strip_parameters(ob.save_model_to_string())
+    nb.free()
+    nd.free()
+
+
 class LogLikelihood:
     """The reference test's FObjTrait (VerifyLightGBMClassifierStream.scala:57-72)."""
 

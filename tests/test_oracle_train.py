@@ -145,3 +145,22 @@ def test_bagging_bag_size_streams_and_out_of_bag_scores(oracle):
         assert t.internal_count[0] == bag and t.leaf_count.sum() == bag
     assert 0.55 * n < bag < 0.65 * n
     assert np.allclose(m.predict_raw(X), bst.scores(), rtol=0, atol=1e-12)      # every row is scored, in the bag or not
+
+
+def test_custom_gradients_reproduce_the_builtin_objective(oracle):
+    """TrainOneIter(grad, hess): fed with the gradients the binary objective computes itself, the custom path grows the same trees
+    (no automatic initial score on either side), and the model text carries no objective line."""
+    from helpers import oracle_dataset
+    X, y = S.higgs_shape(15000)
+    base = PQ + " boost_from_average=false"
+    _, dss, _ = oracle_dataset(oracle, X, y, base)
+    a = oracle.Booster(dss, base)
+    b = oracle.Booster(dss, base.replace("objective=binary", "objective=custom"))
+    for _ in range(5):
+        assert not a.update_one_iter()
+        g, h = a.gradients()
+        assert not b.update_one_iter_custom(g, h)
+    ma, mb = a.save_model_to_string(), b.save_model_to_string()
+    assert ma.split("Tree=0\n", 1)[1].split("end of trees")[0] == mb.split("Tree=0\n", 1)[1].split("end of trees")[0]
+    assert np.array_equal(a.scores(), b.scores())
+    assert "objective=binary" in ma and "\nobjective=" not in mb.split("Tree=0")[0]
