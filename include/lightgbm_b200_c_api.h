@@ -113,6 +113,10 @@ int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters);
 /* booster/LightGBMBooster.scala:272-278 (SWIG wrapper LGBM_BoosterSaveModelToStringSWIG grows the buffer and retries) */
 int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration, int feature_importance_type,
                                   int64_t buffer_len, int64_t* out_len, char* out_str);
+/* booster/LightGBMBooster.scala:480-499 (dumpModel; the SWIG wrapper LGBM_BoosterDumpModelSWIG grows the buffer): the model as
+   JSON in upstream's GBDT::DumpModel layout; same buffer protocol as SaveModelToString.  Needs no GPU. */
+int LGBM_BoosterDumpModel(BoosterHandle handle, int start_iteration, int num_iteration, int feature_importance_type,
+                          int64_t buffer_len, int64_t* out_len, char* out_str);
 /* booster/LightGBMBooster.scala:163,193,173,183 */
 int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len);
 int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len);

@@ -966,6 +966,12 @@ void Booster::FeatureImportance(int num_iteration, int importance_type, double* 
   }
 }
 
+std::string Booster::DumpModel(int start_iteration, int num_iteration, int importance_type) const {
+  std::vector<double> imp(std::max(NumTotalFeatures(), 1), 0.0);
+  FeatureImportance(num_iteration, importance_type, imp.data());
+  return ModelToJson(MakeHeader(), models_, start_iteration, num_iteration, imp);
+}
+
 void Booster::TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const {
   const int n = static_cast<int>(models_.size());
   *t0 = std::min(std::max(0, start_iteration), n);

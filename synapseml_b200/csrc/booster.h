@@ -88,6 +88,7 @@ class Booster {
   bool UpdateOneIterCustom(const float* grad, const float* hess);     // host arrays of num_data floats each
   void ResetParameter(const char* params);
   std::string SaveModelToString(int start_iteration, int num_iteration) const;
+  std::string DumpModel(int start_iteration, int num_iteration, int importance_type) const;      // JSON (LGBM_BoosterDumpModel)
   int NumTrees() const { return static_cast<int>(models_.size()); }
   int CurrentIteration() const { return iter_ + num_init_iteration_; }
   // LGBM_BoosterMerge (upstream GBDT::MergeFrom): the other booster's trees go in front of this one's; scores are not touched

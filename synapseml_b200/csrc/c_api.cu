@@ -301,6 +301,15 @@ int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int
   API_END();
 }
 
+int LGBM_BoosterDumpModel(BoosterHandle handle, int start_iteration, int num_iteration, int feature_importance_type,
+                          int64_t buffer_len, int64_t* out_len, char* out_str) {
+  API_BEGIN();
+  const std::string s = static_cast<Booster*>(handle)->DumpModel(start_iteration, num_iteration, feature_importance_type);
+  *out_len = static_cast<int64_t>(s.size()) + 1;
+  if (*out_len <= buffer_len) memcpy(out_str, s.c_str(), *out_len);
+  API_END();
+}
+
 int LGBM_BoosterGetNumClasses(BoosterHandle, int* out_len) { API_BEGIN(); *out_len = 1; API_END(); }
 int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->NumTotalFeatures(); API_END(); }
 int LGBM_BoosterNumModelPerIteration(BoosterHandle, int* out) { API_BEGIN(); *out = 1; API_END(); }

@@ -234,6 +234,87 @@ void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostT
   if (!saw_tree_word) throw std::runtime_error("Model string does not start with 'tree'");
 }
 
+namespace {
+double AvoidInf(double x) { return std::isnan(x) ? 0.0 : x >= 1e300 ? 1e300 : x <= -1e300 ? -1e300 : x; }
+
+void NodeToJson(const HostTree& t, int index, std::string* s) {
+  if (index >= 0) {
+    const int dt = t.decision_type[index];
+    const int mt = (dt >> 2) & 3;
+    *s += "{\"split_index\":" + std::to_string(index) + ",\n";
+    *s += "\"split_feature\":" + std::to_string(t.split_feature[index]) + ",\n";
+    *s += "\"split_gain\":" + G17(AvoidInf(t.split_gain[index])) + ",\n";
+    *s += "\"threshold\":" + G17(AvoidInf(t.threshold[index])) + ",\n";
+    *s += "\"decision_type\":\"<=\",\n";
+    *s += std::string("\"default_left\":") + ((dt & 2) ? "true" : "false") + ",\n";
+    *s += std::string("\"missing_type\":\"") + (mt == 0 ? "None" : mt == 1 ? "Zero" : "NaN") + "\",\n";
+    *s += "\"internal_value\":" + G17(t.internal_value[index]) + ",\n";
+    *s += "\"internal_weight\":" + G17(t.internal_weight[index]) + ",\n";
+    *s += "\"internal_count\":" + std::to_string(t.internal_count[index]) + ",\n";
+    *s += "\"left_child\":";
+    NodeToJson(t, t.left_child[index], s);
+    *s += ",\n\"right_child\":";
+    NodeToJson(t, t.right_child[index], s);
+    *s += "\n}";
+  } else {
+    const int leaf = ~index;
+    *s += "{\"leaf_index\":" + std::to_string(leaf) + ",\n";
+    *s += "\"leaf_value\":" + G17(t.leaf_value[leaf]) + ",\n";
+    *s += "\"leaf_weight\":" + G17(t.leaf_weight[leaf]) + ",\n";
+    *s += "\"leaf_count\":" + std::to_string(t.leaf_count[leaf]) + "\n}";
+  }
+}
+
+std::string JsonEscape(const std::string& v) {
+  std::string o;
+  for (char c : v) { if (c == '"' || c == '\\') o.push_back('\\'); o.push_back(c); }
+  return o;
+}
+}  // namespace
+
+std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration,
+                        const std::vector<double>& importance) {
+  int first = std::max(0, start_iteration);
+  int last = static_cast<int>(trees.size());
+  if (num_iteration > 0) last = std::min(last, first + num_iteration);
+  std::string s = "{\"name\":\"tree\",\n\"version\":\"v3\",\n\"num_class\":1,\n\"num_tree_per_iteration\":1,\n\"label_index\":0,\n";
+  s += "\"max_feature_idx\":" + std::to_string(h.max_feature_idx) + ",\n";
+  if (!h.objective.empty()) s += "\"objective\":\"" + JsonEscape(h.objective) + "\",\n";
+  s += "\"average_output\":false,\n\"feature_names\":[";
+  for (size_t j = 0; j < h.feature_names.size(); ++j) { if (j) s += ","; s += "\"" + JsonEscape(h.feature_names[j]) + "\""; }
+  s += "],\n\"monotone_constraints\":[],\n\"feature_infos\":{";
+  bool first_obj = true;
+  for (size_t j = 0; j < h.feature_infos.size() && j < h.feature_names.size(); ++j) {
+    const std::string& fi = h.feature_infos[j];
+    const size_t colon = fi.find(':');
+    if (fi.size() < 5 || fi[0] != '[' || colon == std::string::npos) continue;      // "none": a trivial feature
+    if (!first_obj) s += ",";
+    first_obj = false;
+    s += "\"" + JsonEscape(h.feature_names[j]) + "\":{\"min_value\":" + fi.substr(1, colon - 1) + ",\"max_value\":" +
+         fi.substr(colon + 1, fi.size() - colon - 2) + ",\"values\":[]}";
+  }
+  s += "},\n\"tree_info\":[";
+  for (int i = first; i < last; ++i) {
+    const HostTree& t = trees[i];
+    if (i > first) s += ",";
+    s += "{\"tree_index\":" + std::to_string(i) + ",\"num_leaves\":" + std::to_string(t.num_leaves) + ",\n\"num_cat\":0,\n";
+    s += "\"shrinkage\":" + G17(t.shrinkage) + ",\n\"tree_structure\":";
+    if (t.num_leaves <= 1) s += "{\"leaf_value\":" + G17(t.leaf_value.empty() ? 0.0 : t.leaf_value[0]) + "}";
+    else NodeToJson(t, 0, &s);
+    s += "}";
+  }
+  s += "],\n\"feature_importances\":{";
+  std::vector<int> order;
+  for (size_t j = 0; j < importance.size() && j < h.feature_names.size(); ++j) if (importance[j] > 0) order.push_back(static_cast<int>(j));
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return importance[a] > importance[b]; });
+  for (size_t k = 0; k < order.size(); ++k) {
+    if (k) s += ",";
+    s += "\"" + JsonEscape(h.feature_names[order[k]]) + "\":" + G17(importance[order[k]]);
+  }
+  s += "}\n}\n";
+  return s;
+}
+
 std::string FormatG17(double v) { return G17(v); }
 std::string FormatG(double v) { return Gs(v); }
 

@@ -35,6 +35,11 @@ struct ModelHeader {
 };
 
 std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration);
+// JSON dump of the same model (upstream GBDT::DumpModel / Tree::ToJSON): what LGBM_BoosterDumpModel returns to
+// lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:480-499 (dumpModel).
+// importance: per real feature, already computed by the caller (split counts or total gains).
+std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration,
+                        const std::vector<double>& importance);
 
 // Inverse of ModelToString for the subset this library writes (num_class = 1, no categorical splits, no linear trees):
 // what LGBM_BoosterLoadModelFromString reads when the Scala side rebuilds a booster from the model string on an executor

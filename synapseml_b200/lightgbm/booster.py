@@ -64,6 +64,18 @@ class LightGBMBooster:
         self.is_finished = fin.value == 1
         return self.is_finished
 
+    def dump_model(self, importance_type="split"):
+        """dumpModel (:480-499): the model as a JSON string (LGBM_BoosterDumpModel, grow-and-retry like saveToString)."""
+        lib = lightgbmlib()
+        n = C.c_int64()
+        buf = C.create_string_buffer(1 << 20)
+        args = (self.booster_handle, C.c_int(0), C.c_int(-1), C.c_int(0 if importance_type == "split" else 1))
+        validate(lib.LGBM_BoosterDumpModel(*args, C.c_int64(len(buf)), C.byref(n), buf), "Booster Dump Model")
+        if n.value > len(buf):
+            buf = C.create_string_buffer(n.value)
+            validate(lib.LGBM_BoosterDumpModel(*args, C.c_int64(len(buf)), C.byref(n), buf), "Booster Dump Model")
+        return buf.value.decode()
+
     def merge_booster(self, model):
         """mergeBooster (:254-258): the trees of the serialized model go in front of this booster's (continued training)."""
         other, n_iter = C.c_void_p(), C.c_int()

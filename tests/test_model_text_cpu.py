@@ -51,3 +51,45 @@ def test_malformed_model_strings_are_rejected(native, bad):
     h, it = C.c_void_p(), C.c_int()
     assert native.LGBM_BoosterLoadModelFromString(bad.encode(), C.byref(it), C.byref(h)) == -1
     assert len(native.LGBM_GetLastError()) > 0
+
+
+def test_dump_model_json_describes_the_same_trees(native):
+    """LGBM_BoosterDumpModel (LightGBMBooster.scala:480-499): valid JSON in upstream's DumpModel layout whose nested nodes are the
+    text model's arrays."""
+    import json
+
+    import numpy as np
+
+    from synapseml_b200.lightgbm.booster import LightGBMBooster
+    from synapseml_b200.lightgbm.model_text import TextModel
+    text = open(os.path.join(GOLDEN, "quant_model.txt")).read()
+    lb = LightGBMBooster(model_str=text)
+    doc = json.loads(lb.dump_model())
+    tm = TextModel(text)
+    assert doc["name"] == "tree" and doc["num_class"] == 1 and doc["max_feature_idx"] == 27
+    assert doc["objective"] == "binary sigmoid:1" and len(doc["feature_names"]) == 28
+    assert set(doc["feature_infos"]) == set(doc["feature_names"]) and doc["feature_infos"]["Column_0"]["min_value"] < doc["feature_infos"]["Column_0"]["max_value"]
+    assert len(doc["tree_info"]) == len(tm.trees)
+
+    def walk(node, t, seen):
+        if "leaf_index" in node:
+            i = node["leaf_index"]
+            assert node["leaf_value"] == t.leaf_value[i] and node["leaf_count"] == t.leaf_count[i]
+            seen["leaves"] += 1
+            return ~i
+        k = node["split_index"]
+        assert node["split_feature"] == t.split_feature[k] and node["threshold"] == t.threshold[k]
+        assert node["internal_count"] == t.internal_count[k] and node["decision_type"] == "<="
+        assert node["default_left"] == bool(t.decision_type[k] & 2)
+        assert node["missing_type"] == ("None", "Zero", "NaN")[(t.decision_type[k] >> 2) & 3]
+        assert walk(node["left_child"], t, seen) == t.left_child[k] and walk(node["right_child"], t, seen) == t.right_child[k]
+        return k
+
+    for info, t in zip(doc["tree_info"], tm.trees):
+        seen = {"leaves": 0}
+        assert info["num_leaves"] == t.num_leaves and info["num_cat"] == 0
+        walk(info["tree_structure"], t, seen)
+        assert seen["leaves"] == t.num_leaves
+    block = text.split("feature_importances:\n")[1].split("\n\n")[0].strip().splitlines()
+    assert {k: int(v) for k, v in doc["feature_importances"].items()} == {l.split("=")[0]: int(l.split("=")[1]) for l in block}
+    lb.free_native_memory()
