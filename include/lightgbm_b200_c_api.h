@@ -149,6 +149,15 @@ int LGBM_B200_BoosterGetQuantGradients(BoosterHandle handle, int8_t* grad, int8_
 int LGBM_B200_BoosterRootHistogram(BoosterHandle handle, int64_t* out /* F_used*256*2 */);
 int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float* out_ms);
 int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable);
+/* measurement hook for the row-binning kernel (K2): copies `nrow` raw rows (the dataset's own first rows, row-major f64) to the
+   device once and times the production kernel re-binning them `repeats` times from that resident copy; ms per pass */
+int LGBM_B200_DatasetTimeBinning(DatasetHandle handle, const double* rows, int32_t nrow, int repeats, float* out_ms);
+/* per-kernel-type CUDA-event timing of the training kernels (measurement only: it serialises the launches) and the booster's
+   set-up timings, returned as one JSON object (same buffer convention as LGBM_BoosterSaveModelToString) */
+int LGBM_B200_BoosterSetProfile(BoosterHandle handle, int enable);
+int LGBM_B200_BoosterGetProfile(BoosterHandle handle, int64_t buffer_len, int64_t* out_len, char* out_str);
+/* all-gather of one value per rank over the TCP star LGBM_NetworkInit opens (CPU-only; for tests of the multi-process path) */
+int LGBM_B200_NetworkAllGatherInt64(int64_t mine, int64_t* out, int* out_rank, int* out_world);
 int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches,
                               int64_t* hist_launches);
 /* batched best-first growth statistics summed over all trees: dependent rounds, leaves expanded, splits kept */

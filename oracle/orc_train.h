@@ -829,10 +829,15 @@ class Booster {
     double init_score = 0.0;
     const bool custom = custom_grad != nullptr;
     if (obj == OBJ_CUSTOM && !custom) throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
-    if (!custom && models.empty() && !shards[0].ds->has_init_score && cfg.boost_from_average && obj != OBJ_LAMBDARANK) {
+    // ObtainAutomaticInitialScore: BoostFromScore, then GlobalSyncUpByMean over machines (every machine holds the same value)
+    auto automatic_init_score = [&]() {
       double v = BoostFromScore();
-      // ObtainAutomaticInitialScore: GlobalSyncUpByMean over machines (every machine holds the same value)
       if (S > 1) { double acc = 0.0; for (int s = 0; s < S; ++s) acc += v; v = acc / S; }
+      return v;
+    };
+    // GBDT::BoostFromAverage (upstream src/boosting/gbdt.cpp)
+    if (!custom && models.empty() && !shards[0].ds->has_init_score && (cfg.boost_from_average || F == 0)) {
+      const double v = automatic_init_score();
       if (std::fabs(v) > kEpsilon) {
         init_score = v;
         for (auto& sh : shards) for (auto& x : sh.score) x += v;
@@ -868,9 +873,13 @@ class Booster {
       }
       if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
     } else if (models.empty()) {
-      double output = need_train ? init_score : BoostFromScore();
-      tree->AsConstantTree(output);
-      for (auto& sh : shards) for (auto& x : sh.score) x += output;
+      // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
+      // (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
+      if (!custom && obj != OBJ_CUSTOM && !cfg.boost_from_average && !shards[0].ds->has_init_score) {
+        init_score = automatic_init_score();
+        for (auto& sh : shards) for (auto& x : sh.score) x += init_score;
+      }
+      tree->AsConstantTree(init_score);
     }
     models.push_back(std::move(tree));
     if (!should_continue) {

@@ -21,15 +21,20 @@
 
 namespace lgb {
 
-constexpr int kMaxBatch = 8;
-
 // Data-parallel learner, histogram exchange over peer memory (NVLink / NVSwitch) instead of an NCCL launch per round: every
-// rank's work areas and a completion flag are mapped into every other rank's address space (CUDA IPC).  The histogram kernel's
-// last CTA publishes "exchange #seq is complete" in its own flag; the split-search kernel waits until all ranks' flags reach
-// seq and then sums the ranks' bins while it loads them — integer sums, so every rank obtains the same totals whatever the
-// order.  The work areas are double-buffered by the parity of seq: a rank can be at most one exchange ahead of its slowest
-// peer (its next search waits for that peer's next histogram), so the buffer it clears for exchange seq + 2 is no longer
-// being read.  (struct PeerTable: booster.h)
+// rank's work areas and mailbox (struct PeerMail / PeerTable: booster.h) are mapped into every other rank's address space (CUDA
+// IPC).  The histogram kernel's last CTA stores "exchange #seq is complete" into every peer's mailbox; the split-search kernel
+// polls its own (local) mailbox until every rank's word has reached seq and then sums the ranks' bins while it loads them —
+// integer sums, so every rank obtains the same totals whatever the order.  Two forms:
+//   * all-to-all (narrow data, a round is latency-bound): every rank sums every feature of every rank and searches all
+//     features redundantly, so all ranks reach the same decision with ONE exchange per round;
+//   * feature-sliced (wide data; the reduce-scatter by feature + all-gather of best splits of upstream's data-parallel
+//     learner): rank g sums and searches only features [f_lo, f_hi) — 1/G of the remote reads and of the search — and stores
+//     its best split per child into every peer's mailbox; the replay kernel takes the best of the G records.
+// The work areas and split records are double-buffered by the parity of seq: a rank can be at most one exchange ahead of its
+// slowest peer (its next search waits for that peer's next histogram), so the buffer it clears for exchange seq + 2 is no
+// longer being read.  A wait is bounded: after PeerTable::timeout_ns, or when a peer has raised its abort word, the kernel
+// sets BatchCtrl::abort and every later kernel of the fit returns at once; the host then fails the call.
 __device__ __forceinline__ unsigned int LoadAcquireSys(const unsigned int* p) {
   unsigned int v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -37,6 +42,11 @@ __device__ __forceinline__ unsigned int LoadAcquireSys(const unsigned int* p) {
 }
 __device__ __forceinline__ void StoreReleaseSys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long GlobalTimerNs() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
 }
 
 struct NodeDev {
@@ -80,12 +90,14 @@ struct BatchCtrl {
   int spec_used;           // expansions beyond the first of each batch so far (statistics)
   int rounds;
   int applied;             // the finished tree has been added to the scores
+  int abort;               // a wait for a peer rank failed: every kernel returns at once, the host raises the error
+  int pad0_;
   unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
   BatchItem batch[kMaxBatch];
   int find_count[kMaxBatch][2];
   unsigned int max_abs_g_bits, max_abs_h_bits;
   double grad_scale, hess_scale, inv_grad_scale, inv_hess_scale;
-  long long hist_rows, hist_launches;
+  long long hist_rows, hist_launches, part_rows;      // statistics, cleared by the host after every tree
   // optional timeline for experiments (LGB_B200_TRACE=1): (event id, %globaltimer ns) pairs written by CTA 0 of every kernel
   long long* trace;
   int trace_n, trace_cap;
@@ -98,12 +110,29 @@ __constant__ int c_trace_on;      // set by the host while LGB_B200_TRACE record
 __device__ __forceinline__ void Trace(BatchCtrl* ctrl, int id) {
   if (!c_trace_on) return;      // a constant-bank read: the disabled case must not put a global load on thread 0's critical path
   if (ctrl->trace == nullptr) return;
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  const unsigned long long t = GlobalTimerNs();
   const int i = atomicAdd(&ctrl->trace_n, 1);
   if (i < ctrl->trace_cap) { ctrl->trace[2 * i] = id; ctrl->trace[2 * i + 1] = static_cast<long long>(t); }
 }
 #define LGB_TRACE(ctrl, id) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) Trace(ctrl, id); } while (0)
+
+__device__ __forceinline__ bool Finished(const BatchCtrl* ctrl) { return (ctrl->done | ctrl->abort) != 0; }
+
+// Waits until *flag (a word of this rank's own mailbox, stored by a peer) has reached seq.  False: gave up (ctrl->abort is set).
+__device__ __forceinline__ bool PeerWait(const unsigned int* flag, unsigned int seq, const PeerTable& pt, BatchCtrl* ctrl) {
+  unsigned long long t0 = 0;
+  for (unsigned int n = 1;; ++n) {
+    if (static_cast<int>(LoadAcquireSys(flag) - seq) >= 0) return true;
+    if ((n & 255u) == 0) {
+      const PeerMail* me = pt.mail[pt.rank];
+      bool dead = *reinterpret_cast<volatile int*>(&ctrl->abort) != 0;
+      for (int r = 0; r < pt.world; ++r) dead |= LoadAcquireSys(&me->abort[r]) != 0;
+      const unsigned long long t = GlobalTimerNs();
+      if (t0 == 0) t0 = t;
+      if (dead || t - t0 > pt.timeout_ns) { ctrl->abort = 1; __threadfence(); return false; }
+    }
+  }
+}
 
 struct ChildGeom {
   int nl, nr;              // rows that went left / right on this GPU
@@ -123,6 +152,38 @@ __device__ __forceinline__ ChildGeom MakeGeom(const BatchItem& it, unsigned long
   g.left_smaller = g.lc < g.rc;
   g.find = it.search != 0 && !(g.rc < P.min_data_in_leaf * 2 && g.lc < P.min_data_in_leaf * 2);      // BeforeFindBestSplit
   return g;
+}
+
+// ------------------------------------------------------------------------------------------------ max |g|, max |h| over all ranks
+// Quantisation scales need the maxima over ALL rows: lane r stores this rank's pair into rank r's mailbox and stamps it with the
+// number of the gradient pass, then waits for rank r's pair in its own mailbox; the warp's maximum replaces the local one.
+// (One warp, ~one NVLink store latency; replaces an NCCL all-reduce launch per iteration.)
+__global__ void k_peer_max(BatchCtrl* ctrl, PeerTable pt, unsigned int pass) {
+  if (ctrl->abort) return;
+  const int lane = threadIdx.x;
+  const unsigned int g = ctrl->max_abs_g_bits, h = ctrl->max_abs_h_bits;
+  unsigned int mg = 0u, mh = 0u;
+  if (lane < pt.world) {
+    PeerMail* dst = pt.mail[lane];
+    dst->max_vals[pass & 1u][pt.rank][0] = g;
+    dst->max_vals[pass & 1u][pt.rank][1] = h;
+    __threadfence_system();
+    StoreReleaseSys(&dst->max_seq[pt.rank], pass);
+    const PeerMail* me = pt.mail[pt.rank];
+    if (PeerWait(&me->max_seq[lane], pass, pt, ctrl)) {
+      mg = *reinterpret_cast<const volatile unsigned int*>(&me->max_vals[pass & 1u][lane][0]);
+      mh = *reinterpret_cast<const volatile unsigned int*>(&me->max_vals[pass & 1u][lane][1]);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {      // non-negative float bit patterns order like unsigned ints
+    mg = max(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    mh = max(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+  }
+  if (lane == 0) { ctrl->max_abs_g_bits = mg; ctrl->max_abs_h_bits = mh; }
+}
+// raises this rank's abort word in every rank's mailbox (host error path)
+__global__ void k_peer_abort(PeerTable pt) {
+  if (threadIdx.x < pt.world) StoreReleaseSys(&pt.mail[threadIdx.x]->abort[pt.rank], 1u);
 }
 
 // ------------------------------------------------------------------------------------------------ init
@@ -243,17 +304,24 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
   LGB_TRACE(ctrl, 20);
   PdlWait();
   LGB_TRACE(ctrl, 21);
-  if (ctrl->done) return;
+  if (Finished(ctrl)) return;
   __syncthreads();
   HistBody<R, BPL, FLT, ROOT>(rm, rm_stride, gh16, ghfix, idx0, idx1, nodes, ctrl, work, work_elems, F, rows_per_flush, row_ctas,
                               blockIdx.x, blockIdx.y, hsm, lane_addr, &sh, P);
   if (pt.world > 0) {      // the CTA that finishes last tells the other ranks that this rank's histograms are complete
+    __shared__ int s_is_last;
     __threadfence();       // this CTA's global atomics are performed (device scope: the local L2 also serves the peers' reads) ...
     __syncthreads();
-    if (threadIdx.x == 0 && atomicAdd(pt.my_count, 1u) == gridDim.x * gridDim.y - 1) {
-      *pt.my_count = 0u;
+    PeerMail* me = pt.mail[pt.rank];
+    if (threadIdx.x == 0) {
+      const bool last = atomicAdd(&me->hist_count, 1u) == gridDim.x * gridDim.y - 1;
+      if (last) me->hist_count = 0u;
+      s_is_last = last;
+    }
+    __syncthreads();
+    if (s_is_last && threadIdx.x < pt.world) {
       __threadfence_system();      // ... and the last CTA publishes all of them system-wide before the flag
-      StoreReleaseSys(pt.my_flag, pt.seq);
+      StoreReleaseSys(&pt.mail[threadIdx.x]->hist_flag[pt.rank], pt.seq);      // one remote store per peer (own mailbox included)
     }
   }
   LGB_TRACE(ctrl, 22);
@@ -275,6 +343,10 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   double* s_gain = s_gain_all[sub]; int* s_feat = s_feat_all[sub]; int* s_idx = s_idx_all[sub];
   const int F = P.num_features;
   const int b = threadIdx.x & (kFindThreads - 1);
+  // feature-sliced exchange: this rank owns features [f_first, f_first + nf) and sends the best of them to every rank
+  const bool sliced = pt != nullptr && pt->world > 0 && pt->sliced != 0;
+  const int f_first = sliced ? pt->f_lo : 0;
+  const int nf = sliced ? pt->f_hi - pt->f_lo : F;
   // ---- which node is this, and what do we know about it
   NodeDev me;              // what gets published for the child (root: only the fields the search needs)
   int node, parent = -1, parent_slot = 0, side = 0;
@@ -303,7 +375,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   }
   me.child_feat[0] = me.child_feat[1] = -1; me.child_count[0] = me.child_count[1] = 0; me.child_gain[0] = me.child_gain[1] = KMINSCORE;
   if (!find) {         // children that are not searched are published by their first unit alone
-    if (f != 0) return;
+    if (f != f_first) return;
     if (b == 0) {
       me.best = EmptySplit(-1, -1);
       nodes[node] = me;
@@ -356,7 +428,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
                          fb + f, spl, &tg, &th, sub);
     if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
   }
-  if (P.reduce_in_select) {
+  if (P.reduce_in_select && !sliced) {
     // the replay kernel picks the child's best feature (SelectReduceChildren); the first unit publishes everything else
     if (f == 0 && b == 0) {
       if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
@@ -375,12 +447,12 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   }
   __threadfence();
   SubSync(sub);
-  if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == F - 1);
+  if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == nf - 1);
   SubSync(sub);
-  if (s_last) {       // the last unit of this child reduces over the features and publishes the child
+  if (s_last) {       // the last unit of this child reduces over the (rank's) features and publishes the child
     __threadfence();
     double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int j = b; j < F; j += kFindThreads) {
+    for (int j = f_first + b; j < f_first + nf; j += kFindThreads) {
       const double g = fb[j].gain; const int rf = fb[j].real_feature;
       if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
     }
@@ -401,13 +473,29 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
         me.int_g = tg; me.int_h = th;
         me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
       }
-      me.best = fb[bi];
-      nodes[node] = me;
-      if (!root) {
-        nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
-        nodes[parent].child_count[side] = me.global_count;
+      if (sliced) {      // the child's best split is chosen by the replay kernel from all ranks' records (SelectReducePeers)
+        me.best = EmptySplit(-1, -1);
+        nodes[node] = me;
+        s_idx[0] = bi;
+      } else {
+        me.best = fb[bi];
+        nodes[node] = me;
+        if (!root) {
+          nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
+          nodes[parent].child_count[side] = me.global_count;
+        }
       }
       ctrl->find_count[root ? 0 : k][c] = 0;
+    }
+    if (sliced) {        // thread r stores this rank's record into rank r's mailbox, then stamps it
+      SubSync(sub);
+      if (b < pt->world) {
+        SplitMail* dst = &pt->mail[b]->split[pt->seq & 1u][root ? 0 : (k * 2 + c)][pt->rank];
+        dst->s = fb[s_idx[0]];
+        dst->tot_g = tg; dst->tot_h = th;
+        __threadfence_system();
+        StoreReleaseSys(&dst->seq, pt->seq);
+      }
     }
   }
   SubSync(sub);       // the sub-block's shared scratch is reused by its next unit
@@ -422,15 +510,20 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   LGB_TRACE(ctrl, 30);
   PdlWait();
   LGB_TRACE(ctrl, 31);
-  if (ctrl->done) return;
+  if (Finished(ctrl)) return;
   const int k = blockIdx.z;
   if (!root && k >= ctrl->batch_n) return;
-  if (pt.world > 0) {      // every rank's histograms of this exchange must be complete
-    if (threadIdx.x < pt.world)
-      while (static_cast<int>(LoadAcquireSys(pt.flag[threadIdx.x]) - pt.seq) < 0) {}
+  int f = blockIdx.x;
+  if (pt.world > 0) {      // every rank's histograms of this exchange must be complete: their words arrive in this rank's own mailbox
+    if (pt.sliced) { f += pt.f_lo; if (f >= pt.f_hi) return; }
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) s_ok = 1;
     __syncthreads();
+    if (threadIdx.x < pt.world && !PeerWait(&pt.mail[pt.rank]->hist_flag[threadIdx.x], pt.seq, pt, ctrl)) s_ok = 0;
+    __syncthreads();
+    if (!s_ok) return;
   }
-  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, blockIdx.x, blockIdx.y, k, 0, &pt);
+  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, 0, &pt);
   LGB_TRACE(ctrl, 32);
 }
 
@@ -560,7 +653,7 @@ __global__ void __launch_bounds__(kPartThreads, 6) k_bt_partition(const uint8_t*
   LGB_TRACE(ctrl, 10);
   PdlWait();
   LGB_TRACE(ctrl, 11);
-  if (ctrl->done) return;
+  if (Finished(ctrl)) return;
   const int bn = ctrl->batch_n;
   __shared__ int s_tiles[kMaxBatch + 1];
   // the histograms of this batch accumulate into work[0..bn) with atomics: clear them here
@@ -653,10 +746,50 @@ __device__ __forceinline__ void SelectReduceChildren(NodeDev* nodes, const Batch
   }
 }
 
+// Feature-sliced exchange: one warp per child of the round that was searched — lane r waits for rank r's record of the child in
+// this rank's own mailbox (stored there by rank r's split search) and the warp takes the best of them (ties: the lower real
+// feature; the ranks' feature ranges are disjoint).  Every rank sees the same G records, so every rank makes the same choice.
+__device__ __forceinline__ void SelectReducePeers(NodeDev* nodes, BatchCtrl* ctrl, const LearnerParams& P, const PeerTable& pt,
+                                                  int after_root, int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  const int units = after_root ? 1 : 2 * ctrl->batch_n;
+  const PeerMail* me = pt.mail[pt.rank];
+  for (int kc = warp; kc < units; kc += kFindThreads / 32) {
+    const int k = kc >> 1, c = kc & 1;
+    int node = 0, parent = -1, side = 0, count = 0;
+    if (!after_root) {
+      const BatchItem& it = ctrl->batch[k];
+      const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
+      if (!g.find) continue;         // published by the split search itself (no candidates)
+      const bool is_left = (c == 0) == g.left_smaller;
+      node = is_left ? it.left : it.right;
+      side = is_left ? 0 : 1;
+      parent = it.node;
+      count = is_left ? g.lc : g.rc;
+    }
+    SplitDev mine;
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    if (lane < pt.world) {
+      const SplitMail* rec = &me->split[pt.seq & 1u][kc][lane];
+      if (PeerWait(&rec->seq, pt.seq, pt, ctrl)) { mine = rec->s; bg = mine.gain; bf = mine.real_feature; bi = lane; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf) || (!SplitBetter(bg, bf, g, rf) && i < bi))) { bg = g; bf = rf; bi = i; }
+    }
+    if (bi >= 0 && lane == bi) nodes[node].best = mine;
+    if (lane == 0 && parent >= 0) {
+      nodes[parent].child_gain[side] = bg; nodes[parent].child_feat[side] = bf; nodes[parent].child_count[side] = count;
+    }
+  }
+}
+
 __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl* ctrl, const TreeArraysDev& T,
                                            const FeatureMetaDev* __restrict__ fmeta, const LearnerParams& P, int max_nodes,
                                            int spec_budget, int max_batch, double* sel_smem_raw, int sub,
-                                           const SplitDev* feat_best, int after_root) {
+                                           const SplitDev* feat_best, int after_root, const PeerTable& pt) {
   __shared__ int s_state, s_nl, s_m, s_count;
   const int L = P.num_leaves;
   const int Lc = (L + 7) & ~7;
@@ -684,7 +817,11 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     pre_nd = avail[tid]; pre_par = T.leaf_parent[tid]; pre_depth = T.leaf_depth[tid]; pre_value = T.leaf_value[tid];
     pre_weight = T.leaf_weight[tid]; pre_count = T.leaf_count[tid];
   }
-  if (P.reduce_in_select) {
+  if (pt.world > 0 && pt.sliced) {
+    SelectReducePeers(nodes, ctrl, P, pt, after_root, tid);
+    SubSync(sub);
+    if (ctrl->abort) return;
+  } else if (P.reduce_in_select) {
     SelectReduceChildren(nodes, ctrl, feat_best, P, after_root, tid);
     SubSync(sub);      // P0 reads the node records just completed (same CTA: the barrier orders them)
   }
@@ -841,6 +978,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       it.left_sum_g = bs.left_sum_g; it.left_sum_h = bs.left_sum_h; it.right_sum_g = bs.right_sum_g; it.right_sum_h = bs.right_sum_h;
       nodes[nd].state = 1; nodes[nd].left = it.left; nodes[nd].right = it.right;      // expanded by the time the next replay runs
       ctrl->batch[pos] = it;
+      atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->part_rows), static_cast<unsigned long long>(it.src_count));
     }
   }
   if (tid == 0) s_count = min(taken, kmax);
@@ -862,14 +1000,14 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
 __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, int* __restrict__ avail, BatchCtrl* __restrict__ ctrl,
                                                    TreeArraysDev T, const FeatureMetaDev* __restrict__ fmeta, LearnerParams P,
                                                    int max_nodes, int spec_budget, int max_batch, const SplitDev* feat_best,
-                                                   int after_root) {
+                                                   int after_root, PeerTable pt) {
   PdlLaunchDependents();
   LGB_TRACE(ctrl, 40);
   PdlWait();
   LGB_TRACE(ctrl, 41);
-  if (ctrl->done) return;
+  if (Finished(ctrl)) return;
   extern __shared__ double sel_smem_raw[];
-  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw, 0, feat_best, after_root);
+  SelectBody(nodes, avail, ctrl, T, fmeta, P, max_nodes, spec_budget, max_batch, sel_smem_raw, 0, feat_best, after_root, pt);
   LGB_TRACE(ctrl, 42);
 }
 
@@ -894,7 +1032,7 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
   __shared__ double s_val[1024];
   __shared__ uint2 s_node[1024];
   const int nl = ctrl->num_leaves;
-  if (!ctrl->done || ctrl->applied || nl <= 1) return;
+  if (!ctrl->done || ctrl->abort || ctrl->applied || nl <= 1) return;
   for (int i = threadIdx.x; i < nl; i += blockDim.x) {
     double v = T.leaf_value[i] * lr;
     const double zt = (double)1e-35f;

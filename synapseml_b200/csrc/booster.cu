@@ -1,6 +1,7 @@
 #include "booster.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <map>
@@ -8,7 +9,6 @@
 #include "batch_tree.cuh"
 #include "kernels.cuh"
 #include "predict_kernel.cuh"
-#include "tree_persist.cuh"
 
 namespace lgb {
 
@@ -82,7 +82,6 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // per miss (the default granularity), which doubles the DRAM traffic of sparse gathers.  A hint; failure is harmless.
   if (getenv("LGB_B200_L2_FETCH_64") == nullptr) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 32);
   net_ = Network::Get();
-  net_->EnsureComm(device_);
   n_ = train->num_data;
   F_ = train->num_features();
   has_weights_ = train->has_weight;
@@ -138,30 +137,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   d_hist_pool_.Alloc(hist_elems * (1 + max_expansions));
   d_hist_work_.Alloc(hist_elems * kMaxBatch * 2);      // two parities (only the first is used without the peer exchange)
   work_stride_ = static_cast<long long>(hist_elems) * kMaxBatch;
-  memset(&peers_, 0, sizeof(peers_));
-  // Every rank reads every rank's bins in this exchange (world x the payload per rank): right for narrow data, where a round is
-  // latency-bound (C2: 8 x 57 KB per rank), wrong for wide data (C5: 8 x 4 MB per rank x 8 ranks = 256 MB per round), which
-  // stays on NCCL's bandwidth-optimal all-reduce until the feature-sliced exchange exists.
-  const double exchange_bytes = static_cast<double>(lp_.quantized ? hist_elems / 2 : hist_elems) * sizeof(long long) * kMaxBatch * net_->world();
-  if (net_->active() && net_->world() <= kMaxPeers && exchange_bytes <= 16.0 * 1024 * 1024 &&
-      (getenv("LGB_B200_PEER_EXCHANGE") == nullptr || atoi(getenv("LGB_B200_PEER_EXCHANGE")) != 0)) {
-    // histogram exchange over peer memory (batch_tree.cuh: PeerTable); falls back to NCCL all-reduce if the mapping fails
-    d_peer_flags_.AllocZero(64);
-    if (net_->ExchangePeerPointers(d_hist_work_.p, &peer_work_) && net_->ExchangePeerPointers(d_peer_flags_.p, &peer_flags_)) {
-      for (int r = 0; r < net_->world(); ++r) {
-        peers_.work[r] = static_cast<const long long*>(peer_work_[r]);
-        peers_.flag[r] = static_cast<const unsigned int*>(peer_flags_[r]);
-      }
-      peers_.my_flag = d_peer_flags_.p;
-      peers_.my_count = d_peer_flags_.p + 32;
-      peers_.world = net_->world();
-      LogInfo("Histogram exchange over peer memory (%d ranks)", peers_.world);
-      if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: exchange over peer memory, %d ranks\n", net_->rank(), peers_.world);
-    } else {
-      LogWarning("Peer memory could not be mapped; histograms are exchanged with NCCL all-reduce");
-      if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: mapping failed, NCCL fallback\n", net_->rank());
-    }
-  }
+  SetupExchange();
   // quantized mode packs (sum g, sum h) of a bin into one int64 (hist_kernel.cuh), float mode keeps two
   work_elems_ = static_cast<int>(lp_.quantized ? hist_elems / 2 : hist_elems);
   LGB_CHECK(!lp_.quantized || static_cast<double>(n_global_) * cfg_.num_grad_quant_bins < 4294967296.0,
@@ -209,18 +185,6 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
   }
-  // single-GPU learner: one cooperative launch per tree (tree_persist.cuh) when the select scratch fits beside the histograms
-  persist_smem_ = kHistSmem + SelectSmemBytes(cfg_.num_leaves);
-  // Measured (C2, B200): 1.46 / 1.51 ms per iteration against 1.28 / 1.27 for the multi-kernel path at 30 / 500 iterations — the
-  // rounds are bound by chains of dependent L2 round trips inside the phases, not by launches — so it is opt-in
-  // (LGB_B200_PERSISTENT=1); it is kept as the base for an in-kernel peer-memory exchange.
-  use_persistent_ = false;
-  if (const char* env = getenv("LGB_B200_PERSISTENT"))
-    use_persistent_ = atoi(env) != 0 && !net_->active() && persist_smem_ <= size_t(227) * 1024;
-  if (use_persistent_) {
-    SetSmem(k_bt_tree<4, 4, false>, persist_smem_); SetSmem(k_bt_tree<2, 4, false>, persist_smem_); SetSmem(k_bt_tree<1, 4, false>, persist_smem_);
-    SetSmem(k_bt_tree<4, 2, true>, persist_smem_); SetSmem(k_bt_tree<2, 2, true>, persist_smem_); SetSmem(k_bt_tree<1, 2, true>, persist_smem_);
-  }
   SetSmem(k_bt_select, SelectSmemBytes(1024));   // the largest tree the learner accepts; launches ask for what their num_leaves needs
 #define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
@@ -230,12 +194,60 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
 
+// Data-parallel learner: how the ranks exchange histograms.  Peer memory (all ranks on one NVLink / NVSwitch node) needs no
+// communicator; only if it cannot be mapped is NCCL loaded and initialised (seconds at 8 ranks, so not on the default path).
+void Booster::SetupExchange() {
+  memset(&peers_, 0, sizeof(peers_));
+  if (!net_->active()) return;
+  const auto t0 = std::chrono::steady_clock::now();
+  const int world = net_->world();
+  const size_t hist_elems = static_cast<size_t>(std::max(F_, 1)) * kBins * 2;
+  const bool want_peer = world <= kMaxPeers && (getenv("LGB_B200_PEER_EXCHANGE") == nullptr || atoi(getenv("LGB_B200_PEER_EXCHANGE")) != 0);
+  if (want_peer) {
+    d_peer_mail_.AllocZero(1);
+    LGB_CUDA(cudaDeviceSynchronize());      // the zeroed mailbox must be in place before any peer can write to it
+    if (net_->ExchangePeerPointers(device_, d_hist_work_.p, &peer_work_) && net_->ExchangePeerPointers(device_, d_peer_mail_.p, &peer_mail_)) {
+      for (int r = 0; r < world; ++r) {
+        peers_.work[r] = static_cast<const long long*>(peer_work_[r]);
+        peers_.mail[r] = static_cast<PeerMail*>(peer_mail_[r]);
+      }
+      peers_.world = world;
+      peers_.rank = net_->rank();
+      peers_.timeout_ns = static_cast<unsigned long long>(std::max(1, net_->timeout_s())) * 1000000000ULL;
+      // Feature-sliced exchange for wide data.  All-to-all moves world x (the round's bins) into every rank and searches every
+      // feature world times: right while a round is latency-bound (C2: 8 x 57 KB per rank), wrong for C5 (8 x 4 MB per rank).
+      const double all_to_all_bytes = static_cast<double>(lp_.quantized ? hist_elems / 2 : hist_elems) * sizeof(long long) * kMaxBatch * world;
+      bool sliced = F_ >= world && all_to_all_bytes > 16.0 * 1024 * 1024;
+      if (const char* env = getenv("LGB_B200_SLICED")) sliced = atoi(env) != 0 && F_ >= world;
+      peers_.sliced = sliced ? 1 : 0;
+      peers_.f_lo = sliced ? static_cast<int>(static_cast<long long>(F_) * peers_.rank / world) : 0;
+      peers_.f_hi = sliced ? static_cast<int>(static_cast<long long>(F_) * (peers_.rank + 1) / world) : F_;
+      LogInfo("Histogram exchange over peer memory (%d ranks, %s)", world, sliced ? "feature-sliced" : "all-to-all");
+      if (getenv("LGB_B200_PEER_DEBUG"))
+        fprintf(stderr, "[peer] rank %d: exchange over peer memory, %d ranks, %s\n", net_->rank(), world, sliced ? "feature-sliced" : "all-to-all");
+    } else {
+      LogWarning("Peer memory could not be mapped; histograms are exchanged with NCCL all-reduce");
+      if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: mapping failed, NCCL fallback\n", net_->rank());
+    }
+  }
+  if (peers_.world == 0) {
+    net_->EnsureNccl(device_);
+    nccl_exchange_ = true;
+    if (getenv("LGB_B200_PEER_DEBUG")) fprintf(stderr, "[peer] rank %d: NCCL all-reduce exchange\n", net_->rank());
+  }
+  setup_ms_.emplace_back("exchange_setup", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+}
+
 Booster::~Booster() {
   if (device_ < 0) return;      // a loaded model that never predicted owns nothing on a GPU
   cudaSetDevice(device_);
   try { ProfReport(); } catch (...) {}
   try { DumpTrace(); } catch (...) {}
-  if (peers_.world > 0) { net_->ClosePeerPointers(peer_work_); net_->ClosePeerPointers(peer_flags_); }
+  if (peers_.world > 0) {
+    // a peer may still be reading this rank's last histograms / writing its mailbox: leave together
+    try { std::vector<long long> all; net_->HostAllGatherInt64(0, &all); } catch (...) {}
+    net_->ClosePeerPointers(peer_work_); net_->ClosePeerPointers(peer_mail_);
+  }
   if (d_nodes_) cudaFree(d_nodes_);
   if (d_ctrl_) cudaFree(d_ctrl_);
   if (stream_) { cudaStreamSynchronize(stream_); cudaStreamDestroy(stream_); }
@@ -256,17 +268,44 @@ void Booster::ProfEnd() {
   if (!prof_) return;
   LGB_CUDA(cudaEventRecord(prof_recs_.back().b, stream_));
 }
-void Booster::ProfReport() {
-  if (!prof_ || prof_recs_.empty()) return;
+void Booster::ProfCollect() {
+  if (prof_recs_.empty()) return;
   LGB_CUDA(cudaStreamSynchronize(stream_));
-  std::map<std::string, std::pair<int, double>> agg;
   for (auto& r : prof_recs_) {
     float ms = 0; cudaEventElapsedTime(&ms, r.a, r.b);
-    agg[r.name].first++; agg[r.name].second += ms;
+    auto it = std::find_if(prof_agg_.begin(), prof_agg_.end(), [&](const auto& e) { return e.first == r.name; });
+    if (it == prof_agg_.end()) { prof_agg_.emplace_back(r.name, std::make_pair(0LL, 0.0)); it = prof_agg_.end() - 1; }
+    it->second.first += 1; it->second.second += ms;
     cudaEventDestroy(r.a); cudaEventDestroy(r.b);
   }
   prof_recs_.clear();
-  for (auto& kv : agg) fprintf(stderr, "[prof] %-16s n=%6d total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second, 1e3 * kv.second.second / kv.second.first);
+}
+void Booster::ProfReport() {
+  if (!prof_ || getenv("LGB_B200_PROFILE") == nullptr) return;
+  ProfCollect();
+  for (auto& kv : prof_agg_)
+    fprintf(stderr, "[prof] %-16s n=%6lld total=%9.3f ms avg=%8.2f us\n", kv.first.c_str(), kv.second.first, kv.second.second,
+            1e3 * kv.second.second / std::max(1LL, kv.second.first));
+}
+void Booster::EnableProfile(bool on) {
+  LGB_CUDA(cudaSetDevice(device_));
+  ProfCollect();
+  prof_ = on;
+}
+// {"setup_ms": {...}, "kernels": {"name": {"launches": n, "ms": t}, ...}, "partition_rows": r}
+std::string Booster::ProfileJson() {
+  LGB_CUDA(cudaSetDevice(device_));
+  ProfCollect();
+  std::string o = "{\"setup_ms\": {";
+  for (size_t i = 0; i < setup_ms_.size(); ++i)
+    o += StrFormat("%s\"%s\": %.3f", i ? ", " : "", setup_ms_[i].first.c_str(), setup_ms_[i].second);
+  o += "}, \"kernels\": {";
+  for (size_t i = 0; i < prof_agg_.size(); ++i)
+    o += StrFormat("%s\"%s\": {\"launches\": %lld, \"ms\": %.6f}", i ? ", " : "", prof_agg_[i].first.c_str(), prof_agg_[i].second.first,
+                   prof_agg_[i].second.second);
+  o += StrFormat("}, \"partition_rows\": %lld, \"exchange\": \"%s\"}", part_rows_total_,
+                 peers_.world > 0 ? (peers_.sliced ? "peer-sliced" : "peer-all-to-all") : nccl_exchange_ ? "nccl" : "none");
+  return o;
 }
 
 void Booster::DumpTrace() {
@@ -444,7 +483,8 @@ void Booster::PrepareGradients(bool absmax_ready) {
     LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
     k_absmax<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, d_ctrl_);
   }
-  if (net_->active()) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
+  if (peers_.world > 0) { k_peer_max<<<1, 32, 0, stream_>>>(d_ctrl_, peers_, ++max_seq_); ++launches_; }
+  else if (nccl_exchange_) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
   k_scales<<<1, 1, 0, stream_>>>(d_ctrl_, lp_);
   k_quantize<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
                                         static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p,
@@ -505,12 +545,13 @@ void Booster::LaunchHist(bool root) {
   ++launches_;
   ++hist_kernel_launches_;
   // data-parallel learner: every rank needs the global histograms of the batch (integer sums: order-independent)
-  if (net_->active() && peers_.world == 0)
+  if (nccl_exchange_)
     net_->AllReduceSumInt64(work, static_cast<size_t>(work_elems_) * (root ? 1 : max_batch_), stream_);
 }
 
 void Booster::LaunchFind(bool root) {
-  dim3 grid(F_, root ? 1 : 2, root ? 1 : max_batch_);
+  const int fgrid = peers_.sliced ? CeilDiv(F_, peers_.world) : F_;      // sliced: the largest feature range of any rank
+  dim3 grid(fgrid, root ? 1 : 2, root ? 1 : max_batch_);
   PeerTable pt = peers_;
   pt.seq = exchange_seq_;
   pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
@@ -528,48 +569,12 @@ void Booster::LaunchFind(bool root) {
 // ~10 us stay on the critical path and the search kernel loses registers.)
 void Booster::LaunchSelect(bool after_root) {
   ProfBegin("select");
+  PeerTable pt = peers_;
+  pt.seq = exchange_seq_;
   LaunchPdl(k_bt_select, dim3(1), dim3(256), SelectSmemBytes(cfg_.num_leaves), stream_, d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, ds_->d_fmeta.p,
-            lp_, max_nodes_, spec_budget_, max_batch_, static_cast<const SplitDev*>(d_feat_best_.p), after_root ? 1 : 0);
+            lp_, max_nodes_, spec_budget_, max_batch_, static_cast<const SplitDev*>(d_feat_best_.p), after_root ? 1 : 0, pt);
   ProfEnd();
   ++launches_;
-}
-
-void Booster::LaunchTreeKernel() {
-  const BinLayout& lay = ds_->layout;
-  const int R = lay.rows_per_step;
-  const bool flt = !lp_.quantized;
-  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
-  TreeKernelArgs a;
-  a.rm = ds_->d_rm.p; a.rm_stride = static_cast<unsigned>(lay.rm_stride);
-  a.cm = ds_->d_cm.p; a.n_pad = static_cast<long long>(ds_->n_pad);
-  a.fmeta = ds_->d_fmeta.p;
-  a.gh16 = d_gh16_.p; a.ghfix = d_ghfix_.p;
-  a.idx0 = d_idx_[0].p; a.idx1 = d_idx_[1].p;
-  a.work = d_hist_work_.p; a.pool = d_hist_pool_.p;
-  a.nodes = d_nodes_; a.avail = d_avail_.p; a.ctrl = d_ctrl_;
-  a.feat_best = d_feat_best_.p; a.splittable = d_splittable_.p;
-  a.T = tree_dev_;
-  a.P = lp_;
-  a.F = F_; a.work_elems = work_elems_;
-  a.tiles = CeilDiv(F_, ft);
-  a.row_ctas = std::max(1, kNumSms / a.tiles);
-  if (flt) {
-    a.rows_per_flush = kFixRowsPerCopy * R;
-  } else {
-    const int qb = cfg_.num_grad_quant_bins;
-    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
-    a.rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
-  }
-  a.max_nodes = max_nodes_; a.spec_budget = spec_budget_; a.max_batch = max_batch_;
-  LGB_CUDA(cudaMemsetAsync(d_hist_work_.p, 0, sizeof(long long) * work_elems_, stream_));
-  const dim3 grid(kNumSms);      // one CTA per SM; tiles * row_ctas <= 148 of them build histograms, all take part in the other phases
-  void* args[] = {&a};
-  const void* fn;
-  if (!flt) fn = R == 4 ? (const void*)k_bt_tree<4, 4, false> : R == 2 ? (const void*)k_bt_tree<2, 4, false> : (const void*)k_bt_tree<1, 4, false>;
-  else fn = R == 4 ? (const void*)k_bt_tree<4, 2, true> : R == 2 ? (const void*)k_bt_tree<2, 2, true> : (const void*)k_bt_tree<1, 2, true>;
-  LGB_CUDA(cudaLaunchCooperativeKernel(fn, grid, dim3(kHistThreads), args, persist_smem_, stream_));
-  ++launches_;
-  ++hist_kernel_launches_;
 }
 
 // One round = expand every leaf of the current batch (partition, histogram of the smaller child, split search for both
@@ -640,13 +645,6 @@ void Booster::TrainTree(HostTree* out) {
                                                   static_cast<int>(bagging_ ? bag_cnt_global_ : n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
   ++launches_;
-  if (use_persistent_ && !time_hist_ && !prof_) {
-    LaunchTreeKernel();
-    LGB_CUDA(cudaEventRecord(ev_rounds_done_, stream_));
-    UpdateScores();
-    LGB_CHECK(FetchTree(out), "the persistent tree kernel returned before the tree was finished");
-    return;
-  }
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
   LaunchSelect(true);
@@ -665,6 +663,19 @@ void Booster::TrainTree(HostTree* out) {
   }
 }
 
+void Booster::CheckAbort(const BatchCtrl& hc) {
+  if (!hc.abort) return;
+  throw std::runtime_error(StrFormat("Data-parallel training aborted on rank %d: another rank failed or did not arrive within %d s "
+                                     "(listen_time_out of LGBM_NetworkInit); this booster cannot continue", net_->rank(), net_->timeout_s()));
+}
+
+void Booster::AbortPeers() {
+  if (peers_.world == 0 || device_ < 0) return;
+  cudaSetDevice(device_);
+  k_peer_abort<<<1, 32, 0, copy_stream_>>>(peers_);
+  cudaStreamSynchronize(copy_stream_);
+}
+
 // Copies the control block and the tree arrays back; false when the tree is not finished yet (more rounds are needed).
 bool Booster::FetchTree(HostTree* t) {
   const int L = cfg_.num_leaves;
@@ -675,12 +686,14 @@ bool Booster::FetchTree(HostTree* t) {
   LGB_CUDA(cudaMemcpyAsync(h_tree_blob_.data(), d_tree_blob_.p, tree_blob_bytes_, cudaMemcpyDeviceToHost, copy_stream_));
   LGB_CUDA(cudaMemcpyAsync(&hc, d_ctrl_, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, copy_stream_));
   LGB_CUDA(cudaStreamSynchronize(copy_stream_));
+  CheckAbort(hc);
   if (!hc.done) return false;
   last_rounds_ = hc.rounds;
+  part_rows_total_ += hc.part_rows;
   rounds_total_ += hc.rounds; expansions_total_ += (hc.num_nodes - 1) / 2; splits_total_ += hc.num_leaves - 1;
   last_rows_visited_ += hc.hist_rows;
   hist_launches_ += hc.hist_launches;
-  LGB_CUDA(cudaMemsetAsync(&d_ctrl_->hist_rows, 0, 2 * sizeof(long long), stream_));
+  LGB_CUDA(cudaMemsetAsync(&d_ctrl_->hist_rows, 0, 3 * sizeof(long long), stream_));
   const int nl = hc.num_leaves;
   t->num_leaves = nl;
   t->shrinkage = 1.0;
@@ -782,7 +795,10 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   const double kEps = 1e-15f;
   double init_score = 0.0;
   const bool custom = custom_grad != nullptr;
-  if (!custom && models_.empty() && !ds_->has_init_score && cfg_.boost_from_average && obj_ != kLambdarank) {
+  // ObtainAutomaticInitialScore (upstream src/boosting/gbdt.cpp): the objective's BoostFromScore over the labels of all machines,
+  // then the mean over machines of what are identical values
+  auto automatic_init_score = [&]() -> double {
+    if (obj_ == kLambdarank || obj_ == kCustom) return 0.0;
     double sums[2];
     BoostFromScoreLocalSums(&sums[0], &sums[1]);
     net_->HostAllReduceSum(sums, 2);
@@ -796,16 +812,24 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
       v = sums[0] / sums[1];
       if (LogLink()) v = v > 0.0 ? std::log(v) : -std::numeric_limits<double>::infinity();      // Common::SafeLog of the mean label
     }
-    if (net_->active()) {   // ObtainAutomaticInitialScore: mean over machines of identical values
+    if (net_->active()) {
       double acc = 0.0;
       for (int s = 0; s < net_->world(); ++s) acc += v;
       v = acc / net_->world();
     }
+    return v;
+  };
+  auto add_to_scores = [&](double v) {
+    k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), v);
+    AddConstantToValidSets(v);
+    ++launches_;
+  };
+  // GBDT::BoostFromAverage
+  if (!custom && models_.empty() && !ds_->has_init_score && (cfg_.boost_from_average || F_ == 0)) {
+    const double v = automatic_init_score();
     if (std::fabs(v) > kEps) {
       init_score = v;
-      k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), v);
-      AddConstantToValidSets(v);
-      ++launches_;
+      add_to_scores(v);
       LogInfo("Start training from score %lf", v);
     }
   }
@@ -831,18 +855,13 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     tree.Shrinkage(cfg_.learning_rate);
     if (std::fabs(init_score) > kEps) tree.AddBias(init_score);
   } else if (models_.empty()) {
-    double output = init_score;
-    if (!need_train_) {
-      double sums[2];
-      BoostFromScoreLocalSums(&sums[0], &sums[1]);
-      net_->HostAllReduceSum(sums, 2);
-      double pavg = std::max<double>(std::min(sums[0] / sums[1], 1.0 - kEps), kEps);
-      output = (obj_ == kBinary) ? std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid : sums[0] / sums[1];
+    // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
+    // (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
+    if (!custom && obj_ != kCustom && !cfg_.boost_from_average && !ds_->has_init_score) {
+      init_score = automatic_init_score();
+      add_to_scores(init_score);
     }
-    tree.AsConstantTree(output);
-    k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), output);
-    AddConstantToValidSets(output);
-    ++launches_;
+    tree.AsConstantTree(init_score);
   }
   // per-iteration histogram timing (only when enabled by the bench / tests)
   if (time_hist_ && hist_events_used_ > 0) {
@@ -1016,6 +1035,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
             "Predict: predict_type %d (feature contributions) is not supported by this library yet", predict_type);
   LGB_CHECK(ncol == NumTotalFeatures(), "Predict: expected %d columns, got %d", NumTotalFeatures(), ncol);
   LGB_CHECK(nrow >= 0, "Predict: negative row count");
+  std::lock_guard<std::mutex> lock(predict_mu_);
   if (device_ < 0) device_ = ResolveDevice(cfg_);
   LGB_CUDA(cudaSetDevice(device_));
   UploadModel();

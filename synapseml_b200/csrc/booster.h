@@ -5,6 +5,7 @@
 #pragma once
 #include <deque>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -15,21 +16,6 @@
 namespace lgb {
 struct NodeDev;
 struct BatchCtrl;
-
-// Peer-memory histogram exchange of the data-parallel learner (described in batch_tree.cuh).  Passed to kernels by value.
-constexpr int kMaxPeers = 8;
-struct PeerTable {
-  const long long* work[kMaxPeers];     // every rank's work allocation (both parities), mapped into this process
-  const unsigned int* flag[kMaxPeers];  // every rank's "histograms of exchange #seq are complete" word
-  unsigned int* my_flag;
-  unsigned int* my_count;               // CTAs of the running histogram kernel that are finished
-  int world;                            // 0: no exchange (single GPU, or the NCCL fallback)
-  unsigned int seq;                     // the exchange this launch belongs to
-  long long parity_off;                 // element offset of this exchange's buffer inside a rank's work allocation
-};
-}  // namespace lgb
-
-namespace lgb {
 
 struct SplitDev {
   double gain;
@@ -42,6 +28,42 @@ struct SplitDev {
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
   long long left_int_g, left_int_h, right_int_g, right_int_h;
   int missing_type, nan_bin;   // of the split feature (nan_bin = -1: none), so that later stages need no feature table lookup
+};
+
+// ---- peer-memory exchange of the data-parallel learner (kernels: batch_tree.cuh) ------------------------------------------
+// All ranks of one NVLink / NVSwitch node map each other's histogram work areas and one PeerMail block (CUDA IPC).  Signals
+// are PUSHED: a rank stores its word into the mailbox of every peer (a remote store over NVLink) and every rank polls its own,
+// local mailbox, so waiting costs no NVLink round trips.
+constexpr int kMaxPeers = 8;
+constexpr int kMaxBatch = 8;          // leaves expanded per round (batch_tree.cuh)
+// The best split a rank found among ITS features for one child of the round (feature-sliced exchange), stamped with the exchange
+// it belongs to.  tot_*: the leaf totals the rank's search saw (the root's come out of the search).
+struct SplitMail {
+  SplitDev s;
+  long long tot_g, tot_h;
+  unsigned int seq;
+  unsigned int pad_[3];
+};
+struct PeerMail {
+  unsigned int hist_flag[kMaxPeers];            // [r]: rank r's histograms of exchange #value are complete
+  unsigned int max_seq[kMaxPeers];              // [r]: rank r's (max |g|, max |h|) of gradient pass #value has arrived
+  unsigned int max_vals[2][kMaxPeers][2];       // [parity of the pass][r] = float bits of (max |g|, max |h|)
+  unsigned int abort[kMaxPeers];                // [r] != 0: rank r gave up (error or time-out); everyone stops waiting
+  unsigned int hist_count;                      // local: CTAs of the running histogram kernel that are finished
+  unsigned int pad_[15];
+  SplitMail split[2][2 * kMaxBatch][kMaxPeers]; // [parity of the exchange][batch slot * 2 + child][r]
+};
+// Passed to kernels by value.
+struct PeerTable {
+  const long long* work[kMaxPeers];     // every rank's work allocation (both parities), mapped into this process
+  PeerMail* mail[kMaxPeers];            // every rank's mailbox; mail[rank] is this rank's own (local memory)
+  int world;                            // 0: no exchange (single GPU, or the NCCL fallback)
+  int rank;
+  unsigned int seq;                     // the exchange this launch belongs to
+  int sliced;                           // 1: rank g reduces and searches only features [f_lo, f_hi) and the best splits are exchanged
+  int f_lo, f_hi;
+  long long parity_off;                 // element offset of this exchange's buffer inside a rank's work allocation
+  unsigned long long timeout_ns;        // a wait for a peer that lasts longer aborts the fit (listen_time_out of LGBM_NetworkInit)
 };
 
 struct LeafDev {
@@ -125,6 +147,11 @@ class Booster {
   double last_hist_ms() const { return last_hist_ms_; }
   int launches() const { return launches_; }
   void EnableHistTiming(bool on) { time_hist_ = on; }
+  // per-kernel-type CUDA-event timing (slower: breaks launch overlap) and the set-up timings, as one JSON object
+  void EnableProfile(bool on);
+  std::string ProfileJson();
+  // tells the other ranks of a data-parallel fit that this one gave up, so that they stop waiting (c_api.cu, on an exception)
+  void AbortPeers();
   void TimerStart();
   float TimerStop();      // ms between TimerStart and now, measured with CUDA events on the launching stream
 
@@ -156,6 +183,9 @@ class Booster {
   DevBuf<signed char> dp_dt_;
   DevBuf<unsigned char> dp_in_;
   void UploadModel();
+  // Scoring entry points are called from many threads on one handle (LightGBMBooster.scala:67-140 keeps per-thread output
+  // buffers for exactly that); the device staging buffers and the stream are per booster, so calls take turns.
+  std::mutex predict_mu_;
   struct ValidSet {
     Dataset* ds = nullptr;
     DevBuf<double> score;
@@ -227,12 +257,13 @@ class Booster {
   int trace_cap_ = 0, trace_from_ = 0;
   // peer-memory histogram exchange (data-parallel learner)
   PeerTable peers_;
-  std::vector<void*> peer_work_, peer_flags_;
-  DevBuf<unsigned int> d_peer_flags_;
-  unsigned int exchange_seq_ = 0;
+  std::vector<void*> peer_work_, peer_mail_;
+  DevBuf<PeerMail> d_peer_mail_;
+  unsigned int exchange_seq_ = 0, max_seq_ = 0;
+  bool nccl_exchange_ = false;       // peer memory could not be mapped: one NCCL all-reduce per round instead
+  void SetupExchange();
+  void CheckAbort(const BatchCtrl& hc);
   long long work_stride_ = 0;
-  bool use_persistent_ = false;
-  size_t persist_smem_ = 0;
   int part_blocks_ = 888;                   // 6 x 148 SMs (k_bt_partition is built for 6 CTAs per SM)
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
@@ -245,6 +276,10 @@ class Booster {
   void ProfBegin(const char* name);
   void ProfEnd();
   void ProfReport();
+  void ProfCollect();
+  std::vector<std::pair<std::string, std::pair<long long, double>>> prof_agg_;      // name -> (launches, ms)
+  std::vector<std::pair<std::string, double>> setup_ms_;                             // booster set-up phases
+  long long part_rows_total_ = 0;                                                    // rows that went through the partition kernel
 
   void InitObjective();
   double BoostFromScoreLocalSums(double* suml, double* sumw) const;
@@ -254,7 +289,6 @@ class Booster {
   void LaunchHist(bool root);
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
-  void LaunchTreeKernel();
   void LaunchSelect(bool after_root);
   void DumpTrace();
   bool FetchTree(HostTree* out);

@@ -273,15 +273,27 @@ int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, B
   API_END();
 }
 
+// A failure inside an iteration of a data-parallel fit is fatal for the whole group: the other ranks are told to stop waiting
+// for this one (Booster::AbortPeers) before the error goes back to the caller.
 int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished) {
   API_BEGIN();
-  *is_finished = static_cast<Booster*>(handle)->UpdateOneIter() ? 1 : 0;
+  try {
+    *is_finished = static_cast<Booster*>(handle)->UpdateOneIter() ? 1 : 0;
+  } catch (...) {
+    static_cast<Booster*>(handle)->AbortPeers();
+    throw;
+  }
   API_END();
 }
 
 int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished) {
   API_BEGIN();
-  *is_finished = static_cast<Booster*>(handle)->UpdateOneIterCustom(grad, hess) ? 1 : 0;
+  try {
+    *is_finished = static_cast<Booster*>(handle)->UpdateOneIterCustom(grad, hess) ? 1 : 0;
+  } catch (...) {
+    static_cast<Booster*>(handle)->AbortPeers();
+    throw;
+  }
   API_END();
 }
 
@@ -381,6 +393,28 @@ int LGBM_B200_BoosterTimeRootHistogram(BoosterHandle handle, int repeats, float*
   API_END();
 }
 int LGBM_B200_BoosterSetHistTiming(BoosterHandle handle, int enable) { API_BEGIN(); static_cast<Booster*>(handle)->EnableHistTiming(enable != 0); API_END(); }
+int LGBM_B200_DatasetTimeBinning(DatasetHandle handle, const double* rows, int32_t nrow, int repeats, float* out_ms) {
+  API_BEGIN();
+  *out_ms = static_cast<Dataset*>(handle)->TimeBinning(rows, nrow, repeats);
+  API_END();
+}
+int LGBM_B200_BoosterSetProfile(BoosterHandle handle, int enable) { API_BEGIN(); static_cast<Booster*>(handle)->EnableProfile(enable != 0); API_END(); }
+int LGBM_B200_BoosterGetProfile(BoosterHandle handle, int64_t buffer_len, int64_t* out_len, char* out_str) {
+  API_BEGIN();
+  const std::string js = static_cast<Booster*>(handle)->ProfileJson();
+  *out_len = static_cast<int64_t>(js.size()) + 1;
+  if (buffer_len >= *out_len) memcpy(out_str, js.c_str(), js.size() + 1);
+  API_END();
+}
+// small host-value all-gather over the network's TCP star (CPU-only; for tests of the multi-process path)
+int LGBM_B200_NetworkAllGatherInt64(int64_t mine, int64_t* out /* num_machines values */, int* out_rank, int* out_world) {
+  API_BEGIN();
+  std::vector<long long> all;
+  Network::Get()->HostAllGatherInt64(mine, &all);
+  for (size_t i = 0; i < all.size(); ++i) out[i] = all[i];
+  *out_rank = Network::Get()->rank(); *out_world = Network::Get()->world();
+  API_END();
+}
 int LGBM_B200_BoosterGetStats(BoosterHandle handle, int64_t* hist_rows_visited, double* hist_ms, int64_t* kernel_launches,
                               int64_t* hist_launches) {
   API_BEGIN();

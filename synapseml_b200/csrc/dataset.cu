@@ -730,8 +730,8 @@ Dataset* Dataset::CreateFromSerializedReference(const void* buf, int32_t len, in
   LGB_CHECK(r.Get<int32_t>() == 1, "Unsupported serialized reference dataset version");
   std::unique_ptr<Dataset> ds(new Dataset());
   ds->param_string = r.GetStr();
-  ds->cfg.Set(params ? params : "");     // params given here win, then the ones the reference was built with
-  ds->cfg.Set(ds->param_string);
+  ds->cfg.Set(ds->param_string);         // the parameters the reference was built with (driver side) ...
+  ds->cfg.Set(params ? params : "");     // ... overridden by the ones given here (the executor's own: gpu_device_id, verbosity, ...)
   g_verbosity = ds->cfg.verbosity;
   ds->device = ResolveDevice(ds->cfg);
   ds->num_total_features = r.Get<int32_t>();
@@ -868,6 +868,38 @@ void Dataset::FlushSlot(PushSlot* s) {
   s->cur ^= 1;
   LGB_CUDA(cudaEventSynchronize(s->ev[s->cur]));   // the buffer we are about to refill must have been consumed
   s->seg_rows = 0;
+}
+
+// Measurement hook (bench.py's K2 line): `nrow` rows of raw values are copied to the device once (untimed) and the production
+// binning kernel is timed, with CUDA events, re-binning the dataset's first `nrow` rows `repeats` times from that resident copy.
+// The rows must be the dataset's own first rows, so the bins that are rewritten do not change.
+float Dataset::TimeBinning(const double* rows, int nrow, int repeats) {
+  LGB_CHECK(finished, "TimeBinning: the dataset must be finished");
+  LGB_CHECK(nrow > 0 && nrow <= num_data && repeats > 0, "TimeBinning: bad arguments");
+  LGB_CUDA(cudaSetDevice(device));
+  const int F = num_features();
+  LGB_CHECK(F > 0, "TimeBinning: no used feature");
+  DevBuf<double> d;
+  d.Alloc(static_cast<size_t>(nrow) * num_total_features);
+  LGB_CUDA(cudaMemcpy(d.p, rows, sizeof(double) * nrow * num_total_features, cudaMemcpyHostToDevice));
+  const long long nblk = (nrow - 1) / K2_ROWS + 1;
+  const int ftiles = CeilDiv(F, K2_FT);
+  dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
+  const size_t smem = sizeof(double) * K2_FT * K2_BSTRIDE + 2 * K2_FT * K2_ROWS;
+  LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  cudaEvent_t e0, e1;
+  LGB_CUDA(cudaEventCreate(&e0)); LGB_CUDA(cudaEventCreate(&e1));
+  k2_bin_rows<<<grid, 256, smem, 0>>>(d.p, nrow, num_total_features, 0, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+  LGB_CUDA(cudaEventRecord(e0, 0));
+  for (int r = 0; r < repeats; ++r)
+    k2_bin_rows<<<grid, 256, smem, 0>>>(d.p, nrow, num_total_features, 0, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+  LGB_CUDA(cudaEventRecord(e1, 0));
+  LGB_CUDA(cudaEventSynchronize(e1));
+  LGB_CUDA(cudaGetLastError());
+  float ms = 0;
+  LGB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return ms / repeats;
 }
 
 void Dataset::PushRows(const void* data, int data_type, int32_t nrow, int32_t ncol, int64_t start_row, const float* lab,

@@ -180,44 +180,153 @@ void Network::LoadNccl() {
 #undef LOAD
 }
 
+namespace {
+void SetSockOpts(int fd, int timeout_s) {
+  int one = 1;
+  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+  timeval tv{timeout_s, 0};
+  setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+  setsockopt(fd, SOL_SOCKET, SO_SNDTIMEO, &tv, sizeof(tv));
+}
+}  // namespace
+
+// Opens the star: rank 0 listens on its own port of the machine list and accepts one connection per other rank (which
+// introduces itself with its rank); the sockets stay open until Free().
 void Network::Init(const char* machines, int local_listen_port, int listen_time_out_s, int num_machines) {
+  std::lock_guard<std::mutex> lock(mu_);
   if (num_machines <= 1) { rank_ = 0; world_ = 1; return; }
-  LGB_CHECK(comm_ == nullptr && world_ == 1, "LGBM_NetworkInit called twice without LGBM_NetworkFree");
+  LGB_CHECK(fds_.empty() && world_ == 1, "LGBM_NetworkInit called twice without LGBM_NetworkFree");
   auto m = ParseMachines(machines ? machines : "");
   LGB_CHECK(static_cast<int>(m.size()) == num_machines, "Machine list has %d entries but num_machines=%d",
             static_cast<int>(m.size()), num_machines);
   const int r = FindRank(m, local_listen_port);
-  LoadNccl();
-  NcclUniqueId id;
-  memset(&id, 0, sizeof(id));
-  if (r == 0) LGB_NCCL(p_GetUniqueId(&id));
-  BroadcastBlob(m, r, listen_time_out_s > 0 ? listen_time_out_s : 120, &id, sizeof(id));
-  memcpy(unique_id_, &id, sizeof(id));
+  const int timeout = listen_time_out_s > 0 ? listen_time_out_s : 120;
+  std::vector<int> fds;
+  try {
+    if (r == 0) {
+      fds.assign(num_machines, -1);
+      int ls = socket(AF_INET, SOCK_STREAM, 0);
+      LGB_CHECK(ls >= 0, "Network: socket() failed");
+      int one = 1;
+      setsockopt(ls, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
+      sockaddr_in addr{};
+      addr.sin_family = AF_INET;
+      addr.sin_addr.s_addr = htonl(INADDR_ANY);
+      addr.sin_port = htons(static_cast<uint16_t>(m[0].second));
+      if (bind(ls, reinterpret_cast<sockaddr*>(&addr), sizeof(addr)) != 0) {
+        close(ls);
+        throw std::runtime_error(StrFormat("Network: cannot bind port %d (%s)", m[0].second, strerror(errno)));
+      }
+      listen(ls, num_machines);
+      timeval tv{timeout, 0};
+      setsockopt(ls, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+      for (int i = 1; i < num_machines; ++i) {
+        int fd = accept(ls, nullptr, nullptr);
+        if (fd < 0) { close(ls); throw std::runtime_error("Network: timed out waiting for the other ranks to connect"); }
+        SetSockOpts(fd, timeout);
+        int32_t who = -1;
+        try { RecvAll(fd, &who, sizeof(who)); } catch (...) { close(fd); close(ls); throw; }
+        if (who < 1 || who >= num_machines || fds[who] >= 0) { close(fd); close(ls); throw std::runtime_error("Network: unexpected rank in the handshake"); }
+        fds[who] = fd;
+      }
+      close(ls);
+    } else {
+      addrinfo hints{}, *res = nullptr;
+      hints.ai_family = AF_INET;
+      hints.ai_socktype = SOCK_STREAM;
+      LGB_CHECK(getaddrinfo(m[0].first.c_str(), std::to_string(m[0].second).c_str(), &hints, &res) == 0 && res,
+                "Network: cannot resolve %s", m[0].first.c_str());
+      auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(timeout);
+      int fd = -1;
+      while (true) {
+        fd = socket(AF_INET, SOCK_STREAM, 0);
+        if (fd >= 0 && connect(fd, res->ai_addr, res->ai_addrlen) == 0) break;
+        if (fd >= 0) close(fd);
+        fd = -1;
+        if (std::chrono::steady_clock::now() > deadline) break;
+        std::this_thread::sleep_for(std::chrono::milliseconds(5));
+      }
+      freeaddrinfo(res);
+      LGB_CHECK(fd >= 0, "Network: cannot connect to rank 0 at %s:%d", m[0].first.c_str(), m[0].second);
+      SetSockOpts(fd, timeout);
+      fds.assign(1, fd);
+      const int32_t who = r;
+      SendAll(fd, &who, sizeof(who));
+    }
+  } catch (...) {
+    for (int fd : fds) if (fd >= 0) close(fd);
+    throw;
+  }
+  fds_ = fds;
   rank_ = r;
   world_ = num_machines;
+  timeout_s_ = timeout;
 }
 
-void Network::EnsureComm(int device) {
-  if (world_ <= 1 || comm_ != nullptr) return;
-  device_ = device;
-  LGB_CUDA(cudaSetDevice(device));
-  NcclUniqueId id;
-  memcpy(&id, unique_id_, sizeof(id));
-  LGB_NCCL(p_CommInitRank(&comm_, world_, id, rank_));
-  LGB_CUDA(cudaMalloc(&scratch_, 4096));
-  LGB_CUDA(cudaStreamCreateWithFlags(&host_stream_, cudaStreamNonBlocking));
+void Network::CloseSockets() {
+  for (int fd : fds_) if (fd >= 0) close(fd);
+  fds_.clear();
 }
 
 void Network::Free() {
+  std::lock_guard<std::mutex> lock(mu_);
   if (comm_) {
     cudaSetDevice(device_);
     p_CommDestroy(comm_);
     comm_ = nullptr;
   }
-  if (scratch_) { cudaFree(scratch_); scratch_ = nullptr; }
-  if (host_stream_) { cudaStreamDestroy(host_stream_); host_stream_ = nullptr; }
+  CloseSockets();
   rank_ = 0;
   world_ = 1;
+}
+
+// Every rank sends `bytes` to rank 0, which answers with the concatenation in rank order.
+void Network::HostAllGatherBytes(const void* mine, size_t bytes, std::vector<unsigned char>* all) {
+  std::lock_guard<std::mutex> lock(mu_);
+  all->assign(bytes * world_, 0);
+  if (world_ <= 1) { memcpy(all->data(), mine, bytes); return; }
+  LGB_CHECK(!fds_.empty(), "Network is not initialised (LGBM_NetworkInit)");
+  if (rank_ == 0) {
+    memcpy(all->data(), mine, bytes);
+    for (int r = 1; r < world_; ++r) RecvAll(fds_[r], all->data() + bytes * r, bytes);
+    for (int r = 1; r < world_; ++r) SendAll(fds_[r], all->data(), all->size());
+  } else {
+    SendAll(fds_[0], mine, bytes);
+    RecvAll(fds_[0], all->data(), all->size());
+  }
+}
+
+void Network::HostAllReduceSum(double* vals, int n) {
+  if (world_ <= 1) return;
+  std::vector<unsigned char> all;
+  HostAllGatherBytes(vals, sizeof(double) * n, &all);
+  const double* a = reinterpret_cast<const double*>(all.data());
+  for (int i = 0; i < n; ++i) {
+    double s = 0.0;
+    for (int r = 0; r < world_; ++r) s += a[static_cast<size_t>(r) * n + i];      // rank order on every rank: identical sums
+    vals[i] = s;
+  }
+}
+
+void Network::HostAllGatherInt64(long long mine, std::vector<long long>* all) {
+  std::vector<unsigned char> raw;
+  HostAllGatherBytes(&mine, sizeof(mine), &raw);
+  all->resize(world_);
+  memcpy(all->data(), raw.data(), sizeof(long long) * world_);
+}
+
+void Network::EnsureNccl(int device) {
+  if (world_ <= 1 || comm_ != nullptr) return;
+  LoadNccl();
+  NcclUniqueId id;
+  memset(&id, 0, sizeof(id));
+  if (rank_ == 0) LGB_NCCL(p_GetUniqueId(&id));
+  std::vector<unsigned char> all;
+  HostAllGatherBytes(&id, sizeof(id), &all);
+  memcpy(&id, all.data(), sizeof(id));      // rank 0's
+  device_ = device;
+  LGB_CUDA(cudaSetDevice(device));
+  LGB_NCCL(p_CommInitRank(&comm_, world_, id, rank_));
 }
 
 void Network::AllReduceSumInt64(long long* buf, size_t n, cudaStream_t stream) {
@@ -233,44 +342,26 @@ void Network::AllGatherBytes(const void* send, void* recv, size_t bytes_per_rank
   LGB_NCCL(p_AllGather(send, recv, bytes_per_rank, kNcclInt8, comm_, stream));
 }
 
-void Network::HostAllReduceSum(double* vals, int n) {
-  if (world_ <= 1) return;
-  LGB_CHECK(comm_ != nullptr, "NCCL communicator is not initialised");
-  LGB_CHECK(n * sizeof(double) <= 4096, "HostAllReduceSum: too many values");
-  LGB_CUDA(cudaSetDevice(device_));
-  LGB_CUDA(cudaMemcpyAsync(scratch_, vals, n * sizeof(double), cudaMemcpyHostToDevice, host_stream_));
-  LGB_NCCL(p_AllReduce(scratch_, scratch_, n, kNcclFloat64, kNcclSum, comm_, host_stream_));
-  LGB_CUDA(cudaMemcpyAsync(vals, scratch_, n * sizeof(double), cudaMemcpyDeviceToHost, host_stream_));
-  LGB_CUDA(cudaStreamSynchronize(host_stream_));
-}
-
-bool Network::ExchangePeerPointers(void* local, std::vector<void*>* peers) {
+bool Network::ExchangePeerPointers(int device, void* local, std::vector<void*>* peers) {
   peers->clear();
   if (world_ <= 1) { peers->push_back(local); return true; }
-  LGB_CUDA(cudaSetDevice(device_));
-  cudaIpcMemHandle_t mine;
-  long long words[sizeof(cudaIpcMemHandle_t) / sizeof(long long)];
-  static_assert(sizeof(cudaIpcMemHandle_t) % sizeof(long long) == 0, "handle size");
-  const bool ok_local = cudaIpcGetMemHandle(&mine, local) == cudaSuccess;
-  if (!ok_local) { cudaGetLastError(); memset(&mine, 0, sizeof(mine)); }
-  memcpy(words, &mine, sizeof(mine));
-  const int nw = static_cast<int>(sizeof(mine) / sizeof(long long));
-  std::vector<std::vector<long long>> all(nw);
-  for (int i = 0; i < nw; ++i) HostAllGatherInt64(words[i], &all[i]);
-  std::vector<long long> oks;
-  HostAllGatherInt64(ok_local ? 1 : 0, &oks);
+  LGB_CUDA(cudaSetDevice(device));
+  struct Msg { cudaIpcMemHandle_t h; int ok; int device; } mine;
+  memset(&mine, 0, sizeof(mine));
+  mine.ok = cudaIpcGetMemHandle(&mine.h, local) == cudaSuccess;
+  if (!mine.ok) cudaGetLastError();
+  mine.device = device;
+  std::vector<unsigned char> all;
+  HostAllGatherBytes(&mine, sizeof(mine), &all);
+  const Msg* msgs = reinterpret_cast<const Msg*>(all.data());
   bool ok = true;
-  for (long long v : oks) ok = ok && v != 0;
+  for (int r = 0; r < world_; ++r) ok = ok && msgs[r].ok != 0;
   peers->assign(world_, nullptr);
   if (ok) {
     for (int r = 0; r < world_; ++r) {
       if (r == rank_) { (*peers)[r] = local; continue; }
-      cudaIpcMemHandle_t h;
-      long long w[sizeof(cudaIpcMemHandle_t) / sizeof(long long)];
-      for (int i = 0; i < nw; ++i) w[i] = all[i][r];
-      memcpy(&h, w, sizeof(h));
       void* p = nullptr;
-      if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+      if (cudaIpcOpenMemHandle(&p, msgs[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
       (*peers)[r] = p;
     }
   }
@@ -286,18 +377,6 @@ bool Network::ExchangePeerPointers(void* local, std::vector<void*>* peers) {
 void Network::ClosePeerPointers(const std::vector<void*>& peers) {
   for (int r = 0; r < static_cast<int>(peers.size()); ++r)
     if (r != rank_ && peers[r] != nullptr) cudaIpcCloseMemHandle(peers[r]);
-}
-
-void Network::HostAllGatherInt64(long long mine, std::vector<long long>* all) {
-  all->assign(world_, mine);
-  if (world_ <= 1) return;
-  LGB_CHECK(comm_ != nullptr, "NCCL communicator is not initialised");
-  LGB_CUDA(cudaSetDevice(device_));
-  long long* d = static_cast<long long*>(scratch_);
-  LGB_CUDA(cudaMemcpyAsync(d + 256, &mine, sizeof(long long), cudaMemcpyHostToDevice, host_stream_));
-  LGB_NCCL(p_AllGather(d + 256, d, sizeof(long long), kNcclInt8, comm_, host_stream_));
-  LGB_CUDA(cudaMemcpyAsync(all->data(), d, sizeof(long long) * world_, cudaMemcpyDeviceToHost, host_stream_));
-  LGB_CUDA(cudaStreamSynchronize(host_stream_));
 }
 
 }  // namespace lgb

@@ -181,6 +181,18 @@ class LightGBMBooster:
         validate(lightgbmlib().LGBM_B200_BoosterTimerStop(self.booster_handle, C.byref(ms)), "timer")
         return ms.value
 
+    def set_profile(self, on):
+        """Per-kernel-type CUDA-event timing of the training kernels (measurement only: it serialises the launches)."""
+        validate(lightgbmlib().LGBM_B200_BoosterSetProfile(self.booster_handle, C.c_int(1 if on else 0)), "profile")
+
+    def get_profile(self):
+        """{"setup_ms": {...}, "kernels": {name: {"launches", "ms"}}, "partition_rows", "exchange"}"""
+        import json
+        n = C.c_int64()
+        buf = C.create_string_buffer(1 << 14)
+        validate(lightgbmlib().LGBM_B200_BoosterGetProfile(self.booster_handle, C.c_int64(len(buf)), C.byref(n), buf), "profile")
+        return json.loads(buf.value.decode())
+
     def set_hist_timing(self, on):
         validate(lightgbmlib().LGBM_B200_BoosterSetHistTiming(self.booster_handle, C.c_int(1 if on else 0)), "hist timing")
 

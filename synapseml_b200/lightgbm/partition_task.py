@@ -37,8 +37,10 @@ class BasePartitionTask:
         dataset = self.prepare_dataset(partitions)
         measures["datasetCreationTime"] = time.time() - t0      # LightGBMPerformance.scala: the executor's dataset phase
         info = ctx.get("network_info")
+        t0 = time.time()
         if info is not None:
             nm.init_lightgbm_network(info)
+        measures["networkInitTime"] = time.time() - t0
         booster = None
         valid_ds = None
         try:
@@ -48,6 +50,7 @@ class BasePartitionTask:
             t0 = time.time()
             booster = train_utils.create_booster(ctx["train_params"], dataset)
             measures["boosterCreationTime"] = time.time() - t0
+            measures["boosterSetupMs"] = booster.get_profile()["setup_ms"]
             if ctx.get("validation_data") is not None:
                 valid_ds = self.generate_validation_dataset(ctx["validation_data"], dataset)
                 booster.add_valid_data(valid_ds)

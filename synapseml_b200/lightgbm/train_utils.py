@@ -25,6 +25,10 @@ def update_one_iteration(train_params, booster, cur_iters):
             return booster.update_one_iteration_custom(gradient, hessian)
         return booster.update_one_iteration()
     except Exception as e:  # noqa: BLE001 - mirrors the reference's catch-all
+        if train_params.generalParams.numMachines > 1:
+            # with several machines a task that stops alone would leave the others waiting for its histograms: the native side
+            # has told them to give up (LGBM_BoosterUpdateOneIter), and the failure is raised here instead of being swallowed
+            raise
         log.warning("LightGBM reached early termination on one task, stopping training on task. "
                     "This message should rarely occur. Inner exception: %s", e)
         return True

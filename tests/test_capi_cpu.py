@@ -70,6 +70,15 @@ r = C.c_int()
 validate(lightgbmlib().LGBM_B200_NetworkBootstrapBlob(info.lightgbm_network_string.encode(), info.local_listen_port, 30, blob, 128, C.byref(r)))
 assert r.value == dist.get_rank(), (r.value, dist.get_rank())
 assert list(blob) == [(7 * i + 3) %% 256 for i in range(128)]
+dist.barrier()
+# LGBM_NetworkInit opens the TCP star that carries the fit's host-side values (no GPU, no NCCL); values come back in rank order
+nm.init_lightgbm_network(info, timeout=30)
+for trial in range(3):
+    out = (C.c_int64 * 2)()
+    rk, wd = C.c_int(), C.c_int()
+    validate(lightgbmlib().LGBM_B200_NetworkAllGatherInt64(C.c_int64(100 * trial + info.rank), out, C.byref(rk), C.byref(wd)))
+    assert (rk.value, wd.value) == (info.rank, 2) and list(out) == [100 * trial, 100 * trial + 1], list(out)
+nm.free_lightgbm_network()
 # row sharding bookkeeping the estimator does under torch.distributed
 counts = [None, None]
 dist.all_gather_object(counts, 1000 + dist.get_rank())
@@ -81,7 +90,7 @@ open(os.path.join(%(out)r, "rank%%d.ok" %% dist.get_rank()), "w").write("ok")
 
 def test_world_size_2_rendezvous_and_unique_id_handoff(native, tmp_path):
     """N > 1 host path on CPU: gloo rendezvous builds the machine list (NetworkManager), then the library's own TCP bootstrap
-    (what LGBM_NetworkInit uses to distribute the NCCL unique id) moves rank 0's blob to rank 1."""
+    moves rank 0's blob to rank 1, and LGBM_NetworkInit's TCP star all-gathers host values in rank order."""
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     master_port = s.getsockname()[1]

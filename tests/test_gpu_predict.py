@@ -123,3 +123,29 @@ def test_regression_and_large_batches(native):
     assert np.array_equal(predict(nb.handle, X, 0), raw)       # regression: no output transform
     nb.free()
     nd.free()
+
+
+def test_concurrent_scoring_on_one_handle(native):
+    """The reference scores from many task threads on ONE booster handle (LightGBMBooster.scala:67-140: thread-local output buffers,
+    shared boosterPtr): concurrent calls must each get the predictions of their own rows."""
+    import threading
+    from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LocalDataFrame
+    X, y = S.higgs_shape(30000)
+    model = LightGBMClassifier(numIterations=10, numLeaves=15, samplingMode="fixed", microBatchSize=4096).fit(LocalDataFrame.from_arrays(X, y))
+    parts = [X[i * 3000:(i + 1) * 3000 + 17 * i] for i in range(8)]
+    want = [model.predict_raw(p) for p in parts]
+    got = [None] * len(parts)
+    errors = []
+
+    def work(i):
+        try:
+            for _ in range(5):
+                got[i] = model.predict_raw(parts[i])
+                assert np.array_equal(got[i], want[i])
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(parts))]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors[0]

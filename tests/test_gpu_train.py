@@ -148,12 +148,34 @@ def test_training_stops_when_no_leaf_can_split(native, oracle):
     nd.free()
 
 
-def test_single_class_shard_gives_constant_model(native, oracle):
+@pytest.mark.parametrize("boost_from_average", ["true", "false"])
+def test_single_class_shard_gives_constant_model(native, oracle, boost_from_average):
+    """GBDT::TrainOneIter's "only add default score one-time" branch: no tree can be trained, the model is one constant tree holding
+    the automatic initial score, and that score enters the training scores exactly once (with or without boost_from_average)."""
     X, _ = S.higgs_shape(2000)
     y = np.ones(2000, dtype=np.float32)
-    params = "objective=binary num_leaves=7 verbosity=-1"
+    params = "objective=binary num_leaves=7 boost_from_average=%s verbosity=-1" % boost_from_average
     nd, nb, ob = train_both(oracle, X, y, params, 2)
     assert strip_parameters(nb.model()) == strip_parameters(ob.save_model_to_string())
+    m = TextModel(nb.model())
+    assert len(m.trees) == 1 and m.trees[0].num_leaves == 1
+    expected = np.log((1 - 1e-15) / 1e-15)        # pavg clamped at 1 - kEpsilon (float32 1e-15)
+    assert np.allclose(m.trees[0].leaf_value, expected, rtol=1e-3)
+    assert np.array_equal(nb.scores(), ob.scores())
+    assert np.allclose(nb.scores(), m.trees[0].leaf_value[0], rtol=0, atol=0)      # once, not twice
+    nb.free()
+    nd.free()
+
+
+def test_constant_features_give_constant_tree_of_the_label_mean(native, oracle):
+    """No usable feature at all (every column trivial): regression starts from the label mean and stops; scores hold it once."""
+    X = np.full((500, 3), 2.5)
+    y = np.arange(500, dtype=np.float32)
+    params = "objective=regression num_leaves=7 min_data_in_leaf=1 verbosity=-1"
+    nd, nb, ob = train_both(oracle, X, y, params, 2)
+    assert strip_parameters(nb.model()) == strip_parameters(ob.save_model_to_string())
+    assert np.array_equal(nb.scores(), ob.scores())
+    assert np.allclose(nb.scores(), y.astype(np.float64).mean())
     nb.free()
     nd.free()
 
@@ -178,24 +200,3 @@ def test_full_size_properties(native):
     assert np.allclose(m.predict_raw(X[sub]), nb.scores()[sub], rtol=0, atol=1e-12)   # score update == tree traversal
     nb.free()
     nd.free()
-
-
-@pytest.mark.parametrize("mode", ["quantized", "float"])
-def test_opt_in_persistent_tree_kernel_gives_the_same_model(native, monkeypatch, mode):
-    """LGB_B200_PERSISTENT=1 grows each tree in one cooperative launch (tree_persist.cuh) from the same phase bodies."""
-    X, y = S.higgs_shape(60000)
-    params = "objective=binary num_leaves=31 max_bin=255 min_data_in_leaf=20 verbosity=-1"
-    if mode == "quantized":
-        params += " use_quantized_grad=true stochastic_rounding=false"
-    models = []
-    for flag in ("0", "1"):
-        monkeypatch.setenv("LGB_B200_PERSISTENT", flag)
-        nd = NativeDataset(X, y, params, micro_batches=[8192])
-        nb = NativeBooster(nd, params)
-        for _ in range(6):
-            nb.update()
-        models.append(strip_parameters(nb.model()))
-        nb.free()
-        nd.free()
-    assert models[0] == models[1]
-
