@@ -322,6 +322,7 @@ def main():
     for _ in range(args.warmup):
         booster.update_one_iteration()
     sa = booster.stats()
+    pa = booster.get_profile()
     clk_path = os.path.join(tempfile.gettempdir(), "bench_clocks_%d.csv" % rank)
     sampler = clocks_sampler_start(clk_path) if rank == 0 else None
     barrier()
@@ -339,6 +340,8 @@ def main():
     value = N * args.steps / (ms_total * 1e-3)
     launches = sb["kernel_launches"] - sa["kernel_launches"]
     growth = {k: (sb[k] - sa[k]) / args.steps for k in ("growth_rounds", "growth_expansions", "growth_splits")}
+    pb = booster.get_profile()
+    growth.update({k: (pb[k] - pa[k]) / args.steps for k in ("rounds_enqueued", "tree_refetches")})
     # second pass of the same length with every histogram launch bracketed by CUDA events on the launching stream (the events
     # break the programmatic overlap between launches, so this pass is a little slower): roofline numbers only
     booster.set_hist_timing(True)

@@ -129,6 +129,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     max_batch_ = env ? std::max(1, std::min(kMaxBatch, atoi(env))) : kMaxBatch;
   }
   if (const char* env = getenv("LGB_B200_PART_BLOCKS")) part_blocks_ = std::max(1, atoi(env));
+  if (const char* env = getenv("LGB_B200_ROUND_SLACK")) round_slack_ = atoi(env);      // experiments
   spec_budget_ = std::max(2 * kMaxBatch, (L - 1) / 2);
   if (const char* env = getenv("LGB_B200_SPEC_BUDGET")) spec_budget_ = std::max(0, atoi(env));      // experiments
   const int max_expansions = (L - 1) + spec_budget_;
@@ -303,7 +304,8 @@ std::string Booster::ProfileJson() {
   for (size_t i = 0; i < prof_agg_.size(); ++i)
     o += StrFormat("%s\"%s\": {\"launches\": %lld, \"ms\": %.6f}", i ? ", " : "", prof_agg_[i].first.c_str(), prof_agg_[i].second.first,
                    prof_agg_[i].second.second);
-  o += StrFormat("}, \"partition_rows\": %lld, \"exchange\": \"%s\"}", part_rows_total_,
+  o += StrFormat("}, \"partition_rows\": %lld, \"rounds_enqueued\": %lld, \"rounds_used\": %lld, \"tree_refetches\": %lld, \"exchange\": \"%s\"}",
+                 part_rows_total_, rounds_enqueued_, static_cast<long long>(rounds_total_), refetches_,
                  peers_.world > 0 ? (peers_.sliced ? "peer-sliced" : "peer-all-to-all") : nccl_exchange_ ? "nccl" : "none");
   return o;
 }
@@ -648,8 +650,11 @@ void Booster::TrainTree(HostTree* out) {
   ProfBegin("hist_root"); LaunchHist(true); ProfEnd();
   ProfBegin("find"); LaunchFind(true); ProfEnd();
   LaunchSelect(true);
-  // the number of rounds a tree needs is only known on the device: enqueue as many as the previous tree used (+1), then look
-  int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + 1) : std::min(L - 1, (L - 1) / 2 + 2);
+  // The number of rounds a tree needs is only known on the device.  Rounds enqueued beyond it return at once but still cost a
+  // launch each (~2.5 us per kernel, 4 kernels), a tree that is not finished costs a host round trip (~20 us): enqueue what the
+  // previous tree used + round_slack_, then look, and top up two rounds at a time.
+  int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + round_slack_) : std::min(L - 1, (L - 1) / 2 + 2);
+  rounds = std::max(rounds, 1);
   int total = 0;
   while (true) {
     EnqueueRounds(rounds);
@@ -658,9 +663,11 @@ void Booster::TrainTree(HostTree* out) {
     total += rounds;
     LGB_CUDA(cudaGetLastError());
     if (FetchTree(out)) break;
+    ++refetches_;
     LGB_CHECK(total < 2 * L, "tree growth did not finish");   // cannot happen: every round commits at least one split
-    rounds = std::max(1, std::min(L - 1, (L - 1) / 4));
+    rounds = std::min(L - 1, 2);
   }
+  rounds_enqueued_ += total;
 }
 
 void Booster::CheckAbort(const BatchCtrl& hc) {

@@ -222,7 +222,8 @@ class Booster {
   NodeDev* d_nodes_ = nullptr;       // [max_nodes_]
   BatchCtrl* d_ctrl_ = nullptr;
   DevBuf<int> d_avail_;              // leaf id of the committed tree -> node
-  int max_nodes_ = 0, spec_budget_ = 0, max_batch_ = 4, last_rounds_ = 0;
+  int max_nodes_ = 0, spec_budget_ = 0, max_batch_ = 4, last_rounds_ = 0, round_slack_ = 1;
+  long long rounds_enqueued_ = 0, refetches_ = 0;
   DevBuf<SplitDev> d_feat_best_;     // [2][F]
   DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
   DevBuf<unsigned char> d_feature_mask_; // [F] this tree's column sample (feature_fraction < 1 only)
@@ -256,7 +257,7 @@ class Booster {
   DevBuf<long long> d_trace_;
   int trace_cap_ = 0, trace_from_ = 0;
   // peer-memory histogram exchange (data-parallel learner)
-  PeerTable peers_;
+  PeerTable peers_{};
   std::vector<void*> peer_work_, peer_mail_;
   DevBuf<PeerMail> d_peer_mail_;
   unsigned int exchange_seq_ = 0, max_seq_ = 0;

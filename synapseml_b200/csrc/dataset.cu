@@ -490,31 +490,42 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
   const double* myb = sb + lane * K2_BSTRIDE;
   for (long long blk = first_blk + blockIdx.x; blk <= last_blk; blk += gridDim.x) {
     const long long r0 = blk * K2_ROWS;
-    // 8 warps x 16 rows
-    #pragma unroll 4
+    // 8 warps x 16 rows.  A value's search is a chain of up to 8 dependent shared-memory loads, so a thread keeps all 16 of its
+    // rows in flight: the loads are issued together and the (branch-free, fixed-length) searches advance in lock step.
+    double val[16];
+    int lo_[16], hi_[16];
+    #pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const long long row = r0 + warp * 16 + k;
+      const bool in = fi < f_used && row >= start_row && row < start_row + nrow;
+      val[k] = in ? data[(row - start_row) * (long long)ncol + real] : 0.0;
+      lo_[k] = 0;
+      hi_[k] = in ? (missing_type == kMissingNaN ? num_bin - 2 : num_bin - 1) : 0;
+    }
+    #pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      if (val[k] != val[k]) {      // NaN: the last bin when the feature has a NaN bin, else it is binned as 0.0
+        if (missing_type == kMissingNaN) { lo_[k] = hi_[k] = num_bin - 1; }
+        else val[k] = 0.0;
+      }
+    }
+    #pragma unroll
+    for (int step = 0; step < 8; ++step) {      // num_bin <= 256: at most 8 halvings
+      #pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int l = lo_[k], r = hi_[k];
+        const int m = (r + l - 1) >> 1;
+        const bool go = l < r;
+        const bool le = val[k] <= myb[go ? m : 0];
+        hi_[k] = (go && le) ? m : r;
+        lo_[k] = (go && !le) ? m + 1 : l;
+      }
+    }
+    #pragma unroll
     for (int k = 0; k < 16; ++k) {
       const int rr = warp * 16 + k;
-      const long long row = r0 + rr;
-      int bin = 0;
-      if (fi < f_used && row >= start_row && row < start_row + nrow) {
-        double value = data[(row - start_row) * (long long)ncol + real];
-        if (value != value) {
-          if (missing_type == kMissingNaN) { bin = num_bin - 1; goto done; }
-          value = 0.0;
-        }
-        {
-          int l = 0, r = num_bin - 1;
-          if (missing_type == kMissingNaN) r -= 1;
-          while (l < r) {
-            const int m = (r + l - 1) >> 1;
-            if (value <= myb[m]) r = m; else l = m + 1;
-          }
-          bin = l;
-        }
-      }
-    done:
-      tile_cm[lane * K2_ROWS + rr] = (uint8_t)bin;
-      tile_rm[rr * K2_FT + lane] = (uint8_t)bin;
+      tile_cm[lane * K2_ROWS + rr] = (uint8_t)lo_[k];
+      tile_rm[rr * K2_FT + lane] = (uint8_t)lo_[k];
     }
     __syncthreads();
     const bool full = (r0 >= start_row) && (r0 + K2_ROWS <= start_row + nrow);
