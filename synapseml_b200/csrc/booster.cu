@@ -107,6 +107,9 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
   // search's last unit does, as for wide data)
   lp_.reduce_in_select = F_ <= 32 && !(getenv("LGB_B200_REDUCE_IN_SELECT") && atoi(getenv("LGB_B200_REDUCE_IN_SELECT")) == 0);
+  // partition + histogram of the chosen child in one kernel (batch_tree.cuh: k_bt_expand); LGB_B200_FUSED=0: two kernels
+  fused_ = !(getenv("LGB_B200_FUSED") && atoi(getenv("LGB_B200_FUSED")) == 0);
+  lp_.fused = fused_ ? 1 : 0;
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -191,6 +194,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
 #undef SET_HIST_SMEM
+  // the fused kernel keeps a row list per warp behind the histograms: (tile rows + 32) entries of 8 (quantized) / 16 (float) bytes
+  expand_smem_ = kHistSmem + (kHistThreads / 32) * (lp_.quantized ? (4 * 32 + 32) * 8 : (2 * 32 + 32) * 16);
+  SetSmem(k_bt_expand<4, 4, false>, expand_smem_); SetSmem(k_bt_expand<2, 4, false>, expand_smem_); SetSmem(k_bt_expand<1, 4, false>, expand_smem_);
+  SetSmem(k_bt_expand<4, 2, true>, expand_smem_); SetSmem(k_bt_expand<2, 2, true>, expand_smem_); SetSmem(k_bt_expand<1, 2, true>, expand_smem_);
   LGB_CUDA(cudaStreamSynchronize(stream_));
   prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
@@ -513,8 +520,11 @@ void Booster::LaunchHist(bool root) {
     rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
   }
   // non-root launches find their work areas already cleared by k_bt_part_scatter
+  // the work areas alternate between two buffers from one histogram launch to the next (peer exchange: batch_tree.cuh; fused
+  // expansion: the split search clears the buffer of the next launch)
   PeerTable pt = peers_;
-  if (pt.world > 0) { ++exchange_seq_; pt.seq = exchange_seq_; }
+  ++exchange_seq_;
+  pt.seq = exchange_seq_;
   long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
   if (root) LGB_CUDA(cudaMemsetAsync(work, 0, sizeof(long long) * work_elems_, stream_));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -558,12 +568,14 @@ void Booster::LaunchFind(bool root) {
   pt.seq = exchange_seq_;
   pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
   long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
+  long long* clear = fused_ ? d_hist_work_.p + ((exchange_seq_ + 1u) & 1u) * work_stride_ : nullptr;
+  const long long clear_elems = static_cast<long long>(work_elems_) * max_batch_;
   if (lp_.quantized)
     LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt, clear, clear_elems);
   else
     LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt, clear, clear_elems);
   ++launches_;
 }
 
@@ -584,21 +596,76 @@ void Booster::LaunchSelect(bool after_root) {
 // and returns at once when the tree is finished, so rounds are enqueued without waiting for the GPU.
 void Booster::EnqueueRounds(int rounds) {
   for (int r = 0; r < rounds; ++r) {
-    ProfBegin("partition");
-    // the partition kernel clears the work areas the round's histograms go into: with the peer exchange that is the other parity
-    long long* next_work = d_hist_work_.p + (peers_.world > 0 ? ((exchange_seq_ + 1u) & 1u) * work_stride_ : 0);
-    if (idx_es_ == 2)
-      LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
-    else
-      LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
-    ProfEnd();
-    ProfBegin("hist"); LaunchHist(false); ProfEnd();
+    if (fused_) {
+      ProfBegin("expand"); LaunchExpand(); ProfEnd();
+    } else {
+      ProfBegin("partition");
+      // the partition kernel clears the work areas the round's histograms go into
+      long long* next_work = d_hist_work_.p + ((exchange_seq_ + 1u) & 1u) * work_stride_;
+      if (idx_es_ == 2)
+        LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                  d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
+      else
+        LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                  d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
+      ProfEnd();
+      ProfBegin("hist"); LaunchHist(false); ProfEnd();
+      launches_ += 1;
+    }
     ProfBegin("find"); LaunchFind(false); ProfEnd();
     LaunchSelect(false);
-    launches_ += 1;
   }
+}
+
+// Partition + histogram of the chosen child for every leaf of the batch (k_bt_expand).
+void Booster::LaunchExpand() {
+  const BinLayout& lay = ds_->layout;
+  const int R = lay.rows_per_step;
+  const bool flt = !lp_.quantized;
+  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
+  const int tiles = CeilDiv(F_, ft);
+  const int row_ctas = std::max(1, kNumSms / tiles);
+  dim3 grid(row_ctas, tiles);
+  int rows_per_flush;
+  if (flt) {
+    rows_per_flush = kFixRowsPerCopy * R;
+  } else {
+    const int qb = cfg_.num_grad_quant_bins;
+    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
+    rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
+  }
+  PeerTable pt = peers_;
+  ++exchange_seq_;
+  pt.seq = exchange_seq_;
+  long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (time_hist_) {
+    if (hist_events_used_ == hist_events_.size()) {
+      cudaEvent_t a, b;
+      LGB_CUDA(cudaEventCreate(&a)); LGB_CUDA(cudaEventCreate(&b));
+      hist_events_.emplace_back(a, b);
+    }
+    e0 = hist_events_[hist_events_used_].first; e1 = hist_events_[hist_events_used_].second;
+    ++hist_events_used_;
+    LGB_CUDA(cudaEventRecord(e0, stream_));
+  }
+#define EXPAND_ARGS ds_->d_cm.p, static_cast<long long>(ds_->n_pad), ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, \
+                    d_idx_[0].p, d_idx_[1].p, d_ctrl_, work, work_elems_, F_, rows_per_flush, lp_, pt
+  if (!flt) {
+    if (R == 4) LaunchPdl(k_bt_expand<4, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+    else if (R == 2) LaunchPdl(k_bt_expand<2, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+    else LaunchPdl(k_bt_expand<1, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+  } else {
+    if (R == 4) LaunchPdl(k_bt_expand<4, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+    else if (R == 2) LaunchPdl(k_bt_expand<2, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+    else LaunchPdl(k_bt_expand<1, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
+  }
+#undef EXPAND_ARGS
+  LGB_CUDA(cudaGetLastError());
+  if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
+  ++launches_;
+  ++hist_kernel_launches_;
+  if (nccl_exchange_) net_->AllReduceSumInt64(work, static_cast<size_t>(work_elems_) * max_batch_, stream_);
 }
 
 // ColSampler::ResetByTree (upstream src/treelearner/col_sampler.hpp): every tree draws max(round(F * feature_fraction), min(2, F))

@@ -95,6 +95,7 @@ struct LearnerParams {
   int min_data_in_leaf, max_depth, num_leaves, num_features;
   int quantized, dp, num_grad_quant_bins, stochastic_rounding, const_hessian;
   unsigned int seed;
+  int fused;                              // partition + histogram in one kernel (k_bt_expand): the built child is chosen from the estimates
   int reduce_in_select;                   // few features: the replay kernel reduces the per-feature results of a child (no last-arriver
                                           // reduction at the end of the split search)
   const unsigned char* feature_mask;      // [F] 1 = this tree may split on the feature (feature_fraction < 1), nullptr = all
@@ -288,6 +289,9 @@ class Booster {
   void PrepareGradients(bool absmax_ready);           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
+  void LaunchExpand();
+  bool fused_ = true;
+  size_t expand_smem_ = 0;
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
   void LaunchSelect(bool after_root);

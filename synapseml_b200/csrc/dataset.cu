@@ -455,31 +455,32 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
 
 // =====================================================================================================================
 // K2: row binning.  One CTA owns a 32-feature tile and walks 128-row blocks (aligned to absolute row numbers so that
-// the column-major stores are 16-byte aligned).  The tile's bin boundaries sit in shared memory (stride 257 doubles to
-// spread banks); lanes map to features so a warp reads 32 consecutive doubles of one input row; bins go to two shared
-// tiles which are then written out with 128-bit stores: column-major (16 rows of one feature per store) and row-major
-// (16 features of one row per store).
+// the column-major stores are 16-byte aligned).  Lanes map to features, so a warp reads 32 consecutive doubles of one input
+// row.  The tile's bin boundaries sit in shared memory as [bin][feature]: whatever bins the 32 lanes of a warp probe, lane l
+// reads bank pair 2l — the 64-bit loads of a search step never conflict (a [feature][bin] layout with an odd stride
+// serialised them 3-4 ways).  A thread bins 16 consecutive rows of its feature — 16 searches in flight, since a search is a
+// chain of up to 8 dependent shared-memory loads — and stores them as ONE 128-bit word of the column-major matrix straight
+// from registers; the row-major copy goes through a shared tile (conflict-free both ways) and leaves as 16 features of one
+// row per 128-bit store.
 // Algorithmic bytes: N * F * (8 read + 1 write) (+1 for the second layout).
 // =====================================================================================================================
 
 constexpr int K2_ROWS = 128;
 constexpr int K2_FT = 32;
-constexpr int K2_BSTRIDE = 257;
 
 __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ data, int nrow, int ncol, long long start_row,
                                                    const double* __restrict__ bounds, const FeatureMetaDev* __restrict__ fmeta,
                                                    int f_used, uint8_t* __restrict__ cm, long long n_pad,
                                                    uint8_t* __restrict__ rm, int rm_stride) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* sb = reinterpret_cast<double*>(smem_raw);                               // [32][257]
-  uint8_t* tile_cm = smem_raw + sizeof(double) * K2_FT * K2_BSTRIDE;               // [32][128]
-  uint8_t* tile_rm = tile_cm + K2_FT * K2_ROWS;                                    // [128][32]
+  double* sb = reinterpret_cast<double*>(smem_raw);                                       // [256 bins][32 features]
+  uint8_t* tile_rm = smem_raw + sizeof(double) * K2_FT * kMaxBinsPerFeature;              // [128 rows][32 features]
   const int ft = blockIdx.y;
   const int f0 = ft * K2_FT;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < K2_FT * kMaxBinsPerFeature; i += blockDim.x) {
-    int f = i >> 8, b = i & 255;
-    sb[f * K2_BSTRIDE + b] = (f0 + f < f_used) ? bounds[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0.0;
+    const int f = i >> 8, b = i & 255;      // consecutive threads read consecutive bins of one feature (coalesced)
+    sb[b * K2_FT + f] = (f0 + f < f_used) ? bounds[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0.0;
   }
   const int fi = f0 + lane;
   int num_bin = 1, missing_type = 0, real = 0;
@@ -487,11 +488,10 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
   __syncthreads();
   const long long first_blk = start_row / K2_ROWS;
   const long long last_blk = (start_row + nrow - 1) / K2_ROWS;
-  const double* myb = sb + lane * K2_BSTRIDE;
+  const double* myb = sb + lane;
   for (long long blk = first_blk + blockIdx.x; blk <= last_blk; blk += gridDim.x) {
     const long long r0 = blk * K2_ROWS;
-    // 8 warps x 16 rows.  A value's search is a chain of up to 8 dependent shared-memory loads, so a thread keeps all 16 of its
-    // rows in flight: the loads are issued together and the (branch-free, fixed-length) searches advance in lock step.
+    // 8 warps x 16 rows
     double val[16];
     int lo_[16], hi_[16];
     #pragma unroll
@@ -510,40 +510,38 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
       }
     }
     #pragma unroll
-    for (int step = 0; step < 8; ++step) {      // num_bin <= 256: at most 8 halvings
+    for (int step = 0; step < 8; ++step) {      // lower bound over <= 256 bins: at most 8 halvings, branch-free and in lock step
       #pragma unroll
       for (int k = 0; k < 16; ++k) {
         const int l = lo_[k], r = hi_[k];
         const int m = (r + l - 1) >> 1;
         const bool go = l < r;
-        const bool le = val[k] <= myb[go ? m : 0];
+        const bool le = val[k] <= myb[(go ? m : 0) * K2_FT];
         hi_[k] = (go && le) ? m : r;
         lo_[k] = (go && !le) ? m + 1 : l;
       }
     }
+    unsigned int w[4];
     #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      const int rr = warp * 16 + k;
-      tile_cm[lane * K2_ROWS + rr] = (uint8_t)lo_[k];
-      tile_rm[rr * K2_FT + lane] = (uint8_t)lo_[k];
-    }
-    __syncthreads();
+    for (int j = 0; j < 4; ++j)
+      w[j] = static_cast<unsigned>(lo_[4 * j]) | (static_cast<unsigned>(lo_[4 * j + 1]) << 8) | (static_cast<unsigned>(lo_[4 * j + 2]) << 16) |
+             (static_cast<unsigned>(lo_[4 * j + 3]) << 24);
+    #pragma unroll
+    for (int k = 0; k < 16; ++k) tile_rm[(warp * 16 + k) * K2_FT + lane] = static_cast<uint8_t>(lo_[k]);
     const bool full = (r0 >= start_row) && (r0 + K2_ROWS <= start_row + nrow);
-    {  // column-major: thread -> (feature, 16-row chunk)
-      const int f = threadIdx.x >> 3, ch = threadIdx.x & 7;
-      if (f0 + f < f_used) {
-        uint8_t* dst = cm + (long long)(f0 + f) * n_pad + r0 + ch * 16;
-        const uint8_t* src = tile_cm + f * K2_ROWS + ch * 16;
-        if (full) {
-          *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-        } else {
-          for (int j = 0; j < 16; ++j) {
-            long long row = r0 + ch * 16 + j;
-            if (row >= start_row && row < start_row + nrow) dst[j] = src[j];
-          }
+    if (fi < f_used) {      // column-major: this thread's 16 rows of its feature
+      uint8_t* dst = cm + (long long)fi * n_pad + r0 + warp * 16;
+      if (full) {
+        *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+      } else {
+        #pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const long long row = r0 + warp * 16 + k;
+          if (row >= start_row && row < start_row + nrow) dst[k] = static_cast<uint8_t>(lo_[k]);
         }
       }
     }
+    __syncthreads();
     {  // row-major: thread -> (row, 16-feature half)
       const int rr = threadIdx.x >> 1, half = threadIdx.x & 1;
       const long long row = r0 + rr;
@@ -865,7 +863,7 @@ void Dataset::FlushSlot(PushSlot* s) {
     const long long nblk = (s->seg_start + s->seg_rows - 1) / K2_ROWS - s->seg_start / K2_ROWS + 1;
     const int ftiles = CeilDiv(F, K2_FT);
     dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
-    const size_t smem = sizeof(double) * K2_FT * K2_BSTRIDE + 2 * K2_FT * K2_ROWS;
+    const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS;
     static bool attr_set = false;
     if (!attr_set) {
       LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -896,7 +894,7 @@ float Dataset::TimeBinning(const double* rows, int nrow, int repeats) {
   const long long nblk = (nrow - 1) / K2_ROWS + 1;
   const int ftiles = CeilDiv(F, K2_FT);
   dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
-  const size_t smem = sizeof(double) * K2_FT * K2_BSTRIDE + 2 * K2_FT * K2_ROWS;
+  const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS;
   LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   cudaEvent_t e0, e1;
   LGB_CUDA(cudaEventCreate(&e0)); LGB_CUDA(cudaEventCreate(&e1));

@@ -58,11 +58,57 @@ __device__ __forceinline__ void HistUpdate(unsigned bins, unsigned lane_addr, un
   }
 }
 
+// Flush of a CTA's shared histograms (all threads; the caller synchronises before and after): sums the R sub-histograms of each
+// (feature, bin), adds the sum into the global int64 histogram `work` and leaves the shared arrays zero.
+// PACK (quantized mode only): `work` holds ONE int64 per (feature, bin), (sum g << 32) + sum h — valid while the global sum of
+// h stays below 2^32 — so a flush is one global atomic per bin instead of two.
+// Measured (experiments/flush_probe.cu, profiles/r02_flush_probe.log): with 148 CTAs adding into the same 7168 words the flush
+// costs 5.2 us, 1.8 us of it the scan itself; reducing the CTAs of a cluster through distributed shared memory first is slower
+// (8.3 / 16.5 / 24.5 us for clusters of 2 / 4 / 8: DSMEM moves ~20 B per cycle per SM), as are per-CTA slabs + a sum kernel.
+template <int R, int BPL, bool FLT, bool PACK>
+__device__ __forceinline__ void HistFlush(unsigned int* hsm, long long* work, int F, int tile) {
+  constexpr int LPR = 32 / R;
+  constexpr int FT = LPR * BPL;
+  for (int i = threadIdx.x; i < BPL * kBins * LPR; i += blockDim.x) {
+    const int qq = i % LPR;
+    const int bin = (i / LPR) % kBins;
+    const int k = i / (LPR * kBins);
+    const int f = tile * FT + qq * BPL + k;
+    long long g = 0, h = 0;
+    // a warp covers R consecutive bins x LPR lanes; all bins share the banks of a given (sub-histogram, lane), so each thread
+    // starts at a different sub-histogram ((bin + rr) mod R): 32 distinct banks per access instead of an R-way conflict
+    const int skew = (i / LPR) & (R - 1);
+    #pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      const int a = bin * 32 + ((rr + skew) & (R - 1)) * LPR + qq;
+      if (FLT) {
+        g += static_cast<int>(hsm[(2 * k) * (kBins * 32) + a]);
+        h += static_cast<int>(hsm[(2 * k + 1) * (kBins * 32) + a]);
+        hsm[(2 * k) * (kBins * 32) + a] = 0u;
+        hsm[(2 * k + 1) * (kBins * 32) + a] = 0u;
+      } else {
+        const int w = static_cast<int>(hsm[k * (kBins * 32) + a]);
+        h += w & 0xffff;
+        g += w >> 16;
+        hsm[k * (kBins * 32) + a] = 0u;
+      }
+    }
+    if (f < F && (g != 0 || h != 0)) {
+      if (PACK) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(work + static_cast<size_t>(f) * kBins + bin),
+                  static_cast<unsigned long long>(g * 4294967296LL + h));
+      } else {
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
+        if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
+        if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
+      }
+    }
+  }
+}
+
 // Accumulates rows [lo, hi) of a leaf (positions into its index range; ROOT: positions are row ids) into the CTA's shared
 // histograms and flushes them into the global int64 histogram `work` (every rows_per_flush rows and at the end).  The shared
 // arrays must be zero on entry and are zero again on return.  Shared by k_hist and the persistent tree kernel.
-// PACK (quantized mode only): `work` holds ONE int64 per (feature, bin), (sum g << 32) + sum h — valid while the global sum of
-// h stays below 2^32 — so a flush is one global atomic per bin instead of two.
 template <int R, int BPL, bool FLT, bool ROOT, bool PACK = false>
 __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride, const uint16_t* __restrict__ gh16,
                                          const int2* __restrict__ ghfix, const int* idx, int begin, int lo, int hi,
@@ -188,42 +234,7 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       }
     }
     __syncthreads();
-    // flush: sum the R sub-histograms of each (feature, bin) and add into the global int64 histogram
-    for (int i = threadIdx.x; i < BPL * kBins * LPR; i += blockDim.x) {
-      const int qq = i % LPR;
-      const int bin = (i / LPR) % kBins;
-      const int k = i / (LPR * kBins);
-      const int f = tile * FT + qq * BPL + k;
-      long long g = 0, h = 0;
-      // a warp covers R consecutive bins x LPR lanes; all bins share the banks of a given (sub-histogram, lane), so each thread
-      // starts at a different sub-histogram ((bin + rr) mod R): 32 distinct banks per access instead of an R-way conflict
-      const int skew = (i / LPR) & (R - 1);
-      #pragma unroll
-      for (int rr = 0; rr < R; ++rr) {
-        const int a = bin * 32 + ((rr + skew) & (R - 1)) * LPR + qq;
-        if (FLT) {
-          g += static_cast<int>(hsm[(2 * k) * (kBins * 32) + a]);
-          h += static_cast<int>(hsm[(2 * k + 1) * (kBins * 32) + a]);
-          hsm[(2 * k) * (kBins * 32) + a] = 0u;
-          hsm[(2 * k + 1) * (kBins * 32) + a] = 0u;
-        } else {
-          const int w = static_cast<int>(hsm[k * (kBins * 32) + a]);
-          h += w & 0xffff;
-          g += w >> 16;
-          hsm[k * (kBins * 32) + a] = 0u;
-        }
-      }
-      if (f < F && (g != 0 || h != 0)) {
-        if (PACK) {
-          atomicAdd(reinterpret_cast<unsigned long long*>(work + static_cast<size_t>(f) * kBins + bin),
-                    static_cast<unsigned long long>(g * 4294967296LL + h));
-        } else {
-          unsigned long long* dst = reinterpret_cast<unsigned long long*>(work + (static_cast<size_t>(f) * kBins + bin) * 2);
-          if (g != 0) atomicAdd(dst, static_cast<unsigned long long>(g));
-          if (h != 0) atomicAdd(dst + 1, static_cast<unsigned long long>(h));
-        }
-      }
-    }
+    HistFlush<R, BPL, FLT, PACK>(hsm, work, F, tile);
     __syncthreads();
   }
 }
