@@ -185,13 +185,19 @@ class Booster:
             _check(lib().ORC_BoosterSaveModelToString(self.h, C.c_int64(len(buf)), C.byref(n), buf))
         return buf.value.decode()
 
+    def num_class(self):
+        o = C.c_int()
+        _check(lib().ORC_BoosterNumClass(self.h, C.byref(o)))
+        return o.value
+
     def scores(self, shard=0):
-        out = np.zeros(self.datasets[shard].num_data(), dtype=np.float64)
+        """Training scores of one shard; multiclass: class-major [num_class * n]."""
+        out = np.zeros(self.datasets[shard].num_data() * self.num_class(), dtype=np.float64)
         _check(lib().ORC_BoosterGetScores(self.h, C.c_int(shard), _ptr(out, C.c_double)))
         return out
 
     def gradients(self, shard=0):
-        n = self.datasets[shard].num_data()
+        n = self.datasets[shard].num_data() * self.num_class()
         g, h = np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.float32)
         _check(lib().ORC_BoosterGetGradients(self.h, C.c_int(shard), _ptr(g, C.c_float), _ptr(h, C.c_float)))
         return g, h

@@ -139,15 +139,23 @@ int ORC_BoosterSaveModelToString(void* h, int64_t buf_len, int64_t* out_len, cha
 int ORC_BoosterGetScores(void* h, int shard, double* out) {
   ORC_BEGIN
   auto& sh = static_cast<Booster*>(h)->shards.at(shard);
-  std::copy(sh.score.begin(), sh.score.end(), out);
+  if (sh.score_k.empty()) std::copy(sh.score.begin(), sh.score.end(), out);
+  else for (size_t k = 0; k < sh.score_k.size(); ++k) std::copy(sh.score_k[k].begin(), sh.score_k[k].end(), out + k * sh.score_k[k].size());   // class-major
   ORC_END
 }
 
 int ORC_BoosterGetGradients(void* h, int shard, float* g, float* hh) {
   ORC_BEGIN
   auto& sh = static_cast<Booster*>(h)->shards.at(shard);
-  std::copy(sh.grad.begin(), sh.grad.end(), g);
-  std::copy(sh.hess.begin(), sh.hess.end(), hh);
+  if (sh.grad_k.empty()) {
+    std::copy(sh.grad.begin(), sh.grad.end(), g);
+    std::copy(sh.hess.begin(), sh.hess.end(), hh);
+  } else {
+    for (size_t k = 0; k < sh.grad_k.size(); ++k) {      // class-major
+      std::copy(sh.grad_k[k].begin(), sh.grad_k[k].end(), g + k * sh.grad_k[k].size());
+      std::copy(sh.hess_k[k].begin(), sh.hess_k[k].end(), hh + k * sh.hess_k[k].size());
+    }
+  }
   ORC_END
 }
 
@@ -175,3 +183,5 @@ int ORC_SetNumThreads(int n) { ORC_BEGIN if (n > 0) omp_set_num_threads(n); ORC_
 int ORC_GetMaxThreads() { return omp_get_max_threads(); }
 
 }  // extern "C"
+
+extern "C" int ORC_BoosterNumClass(void* h, int* out) { ORC_BEGIN *out = static_cast<orc::Booster*>(h)->K; ORC_END }

@@ -173,6 +173,7 @@ struct Config {
   bool feature_pre_filter = true;
   bool use_quantized_grad = false;
   int num_grad_quant_bins = 4;
+  int num_class = 1;
   bool stochastic_rounding = true;
   bool quant_train_renew_leaf = false;
   int seed = 0;
@@ -287,6 +288,7 @@ struct Config {
     getb("feature_pre_filter", &feature_pre_filter);
     getb("use_quantized_grad", &use_quantized_grad);
     geti("num_grad_quant_bins", &num_grad_quant_bins);
+    geti("num_class", &num_class);
     getb("stochastic_rounding", &stochastic_rounding);
     getb("quant_train_renew_leaf", &quant_train_renew_leaf);
     geti("seed", &seed);
@@ -321,6 +323,7 @@ struct Config {
     if (objective == "regression_l2" || objective == "l2" || objective == "mean_squared_error" || objective == "mse" ||
         objective == "l2_root" || objective == "root_mean_squared_error" || objective == "rmse")
       objective = "regression";
+    if (objective == "softmax") objective = "multiclass";
   }
 };
 

@@ -240,8 +240,10 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
 struct Shard {
   const Dataset* ds = nullptr;
   int64_t row_offset = 0;                 // global row id of local row 0 (for the stochastic-rounding stream)
-  std::vector<double> score;
-  std::vector<score_t> grad, hess;
+  std::vector<double> score;              // scores of the class being trained (multiclass: swapped with score_k[k] around its tree)
+  std::vector<score_t> grad, hess;        // gradients of the tree being trained
+  std::vector<std::vector<double>> score_k;           // multiclass: [class][row]
+  std::vector<std::vector<score_t>> grad_k, hess_k;   // multiclass: [class][row], filled once per iteration
   std::vector<int8_t> qg, qh;             // quantized gradient / hessian
   std::vector<data_size_t> indices, tmp_left, tmp_right;
   std::vector<data_size_t> leaf_begin, leaf_count;
@@ -260,7 +262,11 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS } obj = OBJ_L2;
+  int K = 1;                               // trees per iteration (num_class for multiclass)
+  int cur_class = 0;
+  std::vector<double> class_init_probs;    // multiclass: (weighted) share of every label over all machines
+  std::vector<char> class_need_train;
   bool IsPointRegression() const { return obj == OBJ_L2 || (obj >= OBJ_HUBER && obj <= OBJ_TWEEDIE); }
   bool LogLink() const { return obj == OBJ_POISSON || obj == OBJ_GAMMA || obj == OBJ_TWEEDIE; }
   bool need_train = true;
@@ -376,6 +382,35 @@ class Booster {
       obj = cfg.objective == "poisson" ? OBJ_POISSON : cfg.objective == "gamma" ? OBJ_GAMMA : OBJ_TWEEDIE;
       for (auto& sh : shards) for (float l : sh.ds->label)      // RegressionPoissonLoss::Init / Gamma: label domain
         if (l < 0.0f || (obj == OBJ_GAMMA && l <= 0.0f)) throw std::runtime_error("oracle: " + cfg.objective + " needs non-negative labels");
+    } else if (cfg.objective == "multiclass") {
+      // MulticlassSoftmax::Init (upstream src/objective/multiclass_objective.hpp)
+      obj = OBJ_MULTICLASS;
+      K = cfg.num_class;
+      if (K < 2) throw std::runtime_error("oracle: multiclass needs num_class >= 2");
+      class_init_probs.assign(K, 0.0);
+      double sum_weight = 0.0;
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        for (int64_t i = 0; i < d->num_data; ++i) {
+          const int l = static_cast<int>(d->label[i]);
+          if (l < 0 || l >= K) throw std::runtime_error("oracle: multiclass label outside [0, num_class)");
+          if (has_weights) { class_init_probs[l] += d->weight[i]; sum_weight += d->weight[i]; }
+          else class_init_probs[l] += 1.0;
+        }
+        if (!has_weights) sum_weight += static_cast<double>(d->num_data);
+      }
+      class_need_train.assign(K, 1);
+      for (int k = 0; k < K; ++k) {
+        class_init_probs[k] /= sum_weight;
+        if (std::fabs(class_init_probs[k]) <= kEpsilon || std::fabs(class_init_probs[k]) >= 1.0 - kEpsilon) class_need_train[k] = 0;
+      }
+      for (auto& sh : shards) {
+        const size_t n = sh.score.size();
+        sh.score_k.assign(K, std::vector<double>(n, 0.0));
+        sh.grad_k.assign(K, std::vector<score_t>(n, 0.0f));
+        sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
+        if (sh.ds->has_init_score) throw std::runtime_error("oracle: multiclass init scores are not restated");
+      }
     } else if (cfg.objective == "custom" || cfg.objective == "none") {
       obj = OBJ_CUSTOM;      // no objective function: gradients come from the caller (TrainOneIter(grad, hess))
     } else if (cfg.objective == "lambdarank") {
@@ -435,6 +470,7 @@ class Booster {
 
   double BoostFromScore() const {
     double suml = 0.0, sumw = 0.0;
+    if (obj == OBJ_MULTICLASS) return std::log(std::max<double>(kEpsilon, class_init_probs[cur_class]));
     if (obj == OBJ_BINARY) {
       for (auto& sh : shards) {
         const Dataset* d = sh.ds;
@@ -460,6 +496,7 @@ class Booster {
   }
 
   void GetGradients() {
+    if (obj == OBJ_MULTICLASS) { GetGradientsMulticlass(); return; }
     for (int s = 0; s < S; ++s) {
       Shard& sh = shards[s];
       const Dataset* d = sh.ds;
@@ -602,6 +639,36 @@ class Booster {
     }
   }
 
+  // MulticlassSoftmax::GetGradients: softmax over the row's K scores (Common::Softmax: subtract the maximum, exp, divide by
+  // the sum), g = p - [label == k], h = K / (K - 1) * p * (1 - p); exp is the software function both sides share.
+  void GetGradientsMulticlass() {
+    const double factor = static_cast<double>(K) / (K - 1.0f);
+    for (auto& sh : shards) {
+      const Dataset* d = sh.ds;
+      const int64_t n = d->num_data;
+#pragma omp parallel for schedule(static)
+      for (int64_t i = 0; i < n; ++i) {
+        double rec[64];
+        double wmax = sh.score_k[0][i];
+        for (int k = 0; k < K; ++k) { rec[k] = sh.score_k[k][i]; wmax = std::max(rec[k], wmax); }
+        double wsum = 0.0f;
+        for (int k = 0; k < K; ++k) { rec[k] = SoftExp(rec[k] - wmax); wsum += rec[k]; }
+        for (int k = 0; k < K; ++k) rec[k] /= static_cast<double>(wsum);
+        const int label = static_cast<int>(d->label[i]);
+        for (int k = 0; k < K; ++k) {
+          const double p = rec[k];
+          if (!has_weights) {
+            sh.grad_k[k][i] = label == k ? static_cast<score_t>(p - 1.0f) : static_cast<score_t>(p);
+            sh.hess_k[k][i] = static_cast<score_t>(factor * p * (1.0f - p));
+          } else {
+            sh.grad_k[k][i] = label == k ? static_cast<score_t>((p - 1.0f) * d->weight[i]) : static_cast<score_t>(p * d->weight[i]);
+            sh.hess_k[k][i] = static_cast<score_t>(factor * p * (1.0f - p) * d->weight[i]);
+          }
+        }
+      }
+    }
+  }
+
   // ---------------------------------------------------------------- gradient quantisation (A.6.4)
   void Discretize() {
     double max_g = 0.0, max_h = 0.0;
@@ -625,8 +692,8 @@ class Booster {
         const score_t g = sh.grad[i];
         if (cfg.stochastic_rounding) {
           const uint32_t row = static_cast<uint32_t>(sh.row_offset + i);
-          const float rg = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter), row, 0);
-          const float rh = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter), row, 1);
+          const float rg = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter * K + cur_class), row, 0);
+          const float rh = HashUniform(static_cast<uint32_t>(cfg.seed), static_cast<uint32_t>(iter * K + cur_class), row, 1);
           sh.qg[i] = g >= 0.0f ? static_cast<int8_t>(g * inv_g + rg) : static_cast<int8_t>(g * inv_g - rg);
           sh.qh[i] = static_cast<int8_t>(sh.hess[i] * inv_h + rh);
         } else {
@@ -826,21 +893,39 @@ class Booster {
   // GBDT::TrainOneIter(gradients, hessians): with caller-supplied arrays (one value per row, shard after shard) there is no
   // automatic initial score and the objective's own gradients are not computed
   bool TrainOneIter(const float* custom_grad = nullptr, const float* custom_hess = nullptr) {
-    double init_score = 0.0;
     const bool custom = custom_grad != nullptr;
+    const bool multi = obj == OBJ_MULTICLASS;
     if (obj == OBJ_CUSTOM && !custom) throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
+    if (multi && custom) throw std::runtime_error("oracle: caller-supplied gradients with multiclass are not restated");
+    // multiclass: class k's scores / gradients take the place of the single-class arrays while its tree is handled
+    auto enter_class = [&](int k, bool with_grad) {
+      cur_class = k;
+      if (!multi) return;
+      for (auto& sh : shards) { sh.score.swap(sh.score_k[k]); if (with_grad) { sh.grad.swap(sh.grad_k[k]); sh.hess.swap(sh.hess_k[k]); } }
+    };
+    auto leave_class = [&](int k, bool with_grad) {
+      if (!multi) return;
+      for (auto& sh : shards) { sh.score.swap(sh.score_k[k]); if (with_grad) { sh.grad.swap(sh.grad_k[k]); sh.hess.swap(sh.hess_k[k]); } }
+    };
     // ObtainAutomaticInitialScore: BoostFromScore, then GlobalSyncUpByMean over machines (every machine holds the same value)
     auto automatic_init_score = [&]() {
       double v = BoostFromScore();
       if (S > 1) { double acc = 0.0; for (int s = 0; s < S; ++s) acc += v; v = acc / S; }
       return v;
     };
-    // GBDT::BoostFromAverage (upstream src/boosting/gbdt.cpp)
-    if (!custom && models.empty() && !shards[0].ds->has_init_score && (cfg.boost_from_average || F == 0)) {
-      const double v = automatic_init_score();
-      if (std::fabs(v) > kEpsilon) {
-        init_score = v;
-        for (auto& sh : shards) for (auto& x : sh.score) x += v;
+    // GBDT::BoostFromAverage (upstream src/boosting/gbdt.cpp), once per class
+    std::vector<double> init_scores(K, 0.0);
+    if (!custom) {
+      for (int k = 0; k < K; ++k) {
+        enter_class(k, false);
+        if (models.empty() && !shards[0].ds->has_init_score && (cfg.boost_from_average || F == 0)) {
+          const double v = automatic_init_score();
+          if (std::fabs(v) > kEpsilon) {
+            init_scores[k] = v;
+            for (auto& sh : shards) for (auto& x : sh.score) x += v;
+          }
+        }
+        leave_class(k, false);
       }
     }
     if (custom) {
@@ -850,40 +935,46 @@ class Booster {
         off += sh.grad.size();
       }
     } else {
-      GetGradients();
+      GetGradients();      // Boosting(): all classes at once
     }
     Bagging();
     bool should_continue = false;
-    std::unique_ptr<Tree> tree(new Tree(2));
-    if (need_train && F > 0) tree = TrainTree();
-    if (tree->num_leaves > 1) {
-      should_continue = true;
-      tree->Shrinkage(cfg.learning_rate);
-      for (auto& sh : shards) {
-        for (int l = 0; l < tree->num_leaves; ++l) {
-          const double out = tree->leaf_value[l];
-          const data_size_t b = sh.leaf_begin[l], n = sh.leaf_count[l];
-          for (data_size_t i = 0; i < n; ++i) sh.score[sh.indices[b + i]] += out;
+    for (int k = 0; k < K; ++k) {
+      enter_class(k, true);
+      const bool train_this = multi ? class_need_train[k] != 0 : need_train;
+      std::unique_ptr<Tree> tree(new Tree(2));
+      if (train_this && F > 0) tree = TrainTree();
+      if (tree->num_leaves > 1) {
+        should_continue = true;
+        tree->Shrinkage(cfg.learning_rate);
+        for (auto& sh : shards) {
+          for (int l = 0; l < tree->num_leaves; ++l) {
+            const double out = tree->leaf_value[l];
+            const data_size_t b = sh.leaf_begin[l], n = sh.leaf_count[l];
+            for (data_size_t i = 0; i < n; ++i) sh.score[sh.indices[b + i]] += out;
+          }
+          // out-of-bag rows: ScoreUpdater::AddScore(tree, indices, cnt) walks the tree over the row's bins
+          for (data_size_t i = sh.bag_cnt; bagging && i < static_cast<data_size_t>(sh.ds->num_data); ++i) {
+            const data_size_t r = sh.bag_indices[i];
+            sh.score[r] += tree->leaf_value[LeafByBins(*tree, sh.ds, r)];
+          }
         }
-        // out-of-bag rows: ScoreUpdater::AddScore(tree, indices, cnt) walks the tree over the row's bins
-        for (data_size_t i = sh.bag_cnt; bagging && i < static_cast<data_size_t>(sh.ds->num_data); ++i) {
-          const data_size_t r = sh.bag_indices[i];
-          sh.score[r] += tree->leaf_value[LeafByBins(*tree, sh.ds, r)];
+        if (std::fabs(init_scores[k]) > kEpsilon) tree->AddBias(init_scores[k]);
+      } else if (static_cast<int>(models.size()) < K) {
+        // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the
+        // scores (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
+        if (!custom && obj != OBJ_CUSTOM && !cfg.boost_from_average && !shards[0].ds->has_init_score) {
+          init_scores[k] = automatic_init_score();
+          for (auto& sh : shards) for (auto& x : sh.score) x += init_scores[k];
         }
+        tree->AsConstantTree(init_scores[k]);
       }
-      if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
-    } else if (models.empty()) {
-      // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
-      // (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
-      if (!custom && obj != OBJ_CUSTOM && !cfg.boost_from_average && !shards[0].ds->has_init_score) {
-        init_score = automatic_init_score();
-        for (auto& sh : shards) for (auto& x : sh.score) x += init_score;
-      }
-      tree->AsConstantTree(init_score);
+      models.push_back(std::move(tree));
+      leave_class(k, true);
     }
-    models.push_back(std::move(tree));
+    cur_class = 0;
     if (!should_continue) {
-      if (models.size() > 1) models.pop_back();
+      if (static_cast<int>(models.size()) > K) for (int k = 0; k < K; ++k) models.pop_back();
       return true;
     }
     ++iter;
@@ -912,6 +1003,7 @@ class Booster {
     if (obj == OBJ_BINARY) return "binary sigmoid:" + FmtG(cfg.sigmoid);
     if (obj == OBJ_L2) return "regression";
     if (obj == OBJ_CUSTOM) return "";
+    if (obj == OBJ_MULTICLASS) return "multiclass num_class:" + std::to_string(K);
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }
@@ -921,8 +1013,8 @@ class Booster {
     std::string s;
     s += "tree\n";
     s += "version=v3\n";
-    s += "num_class=1\n";
-    s += "num_tree_per_iteration=1\n";
+    s += "num_class=" + std::to_string(K) + "\n";
+    s += "num_tree_per_iteration=" + std::to_string(K) + "\n";
     s += "label_index=0\n";
     s += "max_feature_idx=" + std::to_string(d->num_total_features - 1) + "\n";
     if (!ObjectiveString().empty()) s += "objective=" + ObjectiveString() + "\n";      // none without an objective function

@@ -149,7 +149,7 @@ __device__ __forceinline__ ChildGeom MakeGeom(const BatchItem& it, unsigned long
   g.lc = P.dp ? it.est_left : g.nl;
   g.rc = P.dp ? it.est_right : g.nr;
   g.buf = it.src_buf < 0 ? 0 : 1 - it.src_buf;
-  g.left_smaller = P.fused ? (it.est_left < it.est_right) : (g.lc < g.rc);      // fused: chosen before the partition (k_bt_expand)
+  g.left_smaller = g.lc < g.rc;
   g.find = it.search != 0 && !(g.rc < P.min_data_in_leaf * 2 && g.lc < P.min_data_in_leaf * 2);      // BeforeFindBestSplit
   return g;
 }
@@ -505,16 +505,8 @@ template <bool QUANT>
 __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
                                                  const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
                                                  BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
-                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt,
-                                                 long long* __restrict__ clear_area, long long clear_elems) {
+                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
   PdlLaunchDependents();
-  // Fused expansion (k_bt_expand): the next round's histograms go into the OTHER parity's work areas, which nobody has read since
-  // the previous search of that parity finished two kernels ago — cleared here, before the wait, under the predecessor's tail.
-  if (clear_area != nullptr) {
-    const long long nthreads = static_cast<long long>(gridDim.x) * gridDim.y * gridDim.z * blockDim.x;
-    const long long me = (static_cast<long long>(blockIdx.z) * gridDim.y + blockIdx.y) * gridDim.x * blockDim.x + blockIdx.x * blockDim.x + threadIdx.x;
-    for (long long i = me; i < clear_elems; i += nthreads) clear_area[i] = 0;
-  }
   LGB_TRACE(ctrl, 30);
   PdlWait();
   LGB_TRACE(ctrl, 31);
@@ -670,324 +662,6 @@ __global__ void __launch_bounds__(kPartThreads, 6) k_bt_partition(const uint8_t*
   if (threadIdx.x == 0) PartTileList(ctrl, bn, s_tiles);
   __syncthreads();
   PartitionTiles<ES>(cm, n_pad, idx0r, idx1r, idx0w, idx1w, gh16, ghfix, ctrl, bn, s_tiles, blockIdx.x, gridDim.x, 0);
-  LGB_TRACE(ctrl, 12);
-}
-
-// ------------------------------------------------------------------------------------------------ K7 + K4 fused
-// One pass over the rows of every leaf of the round does both the partition and the histogram of the smaller child.
-//
-// Which child's histogram is built directly (the other is parent - child, exactly, in integers) does not change any result, so
-// the choice is made BEFORE the partition, from the split's count estimates (the data-parallel learner's global counts; the
-// serial learner's hessian-based estimates): a row's side is known as soon as its bin of the split feature is, and rows of the
-// chosen side go into the CTA's shared histograms in the same pass.  Against partition -> histogram as two kernels this saves
-// one kernel boundary per round, the second read of the index entries, and — the partition being a chain of dependent round
-// trips at a third of the DRAM bandwidth, the histogram a stream of 128-byte gathers — lets each fill the other's bubbles.
-//
-// CTA = kHistThreads threads = 4 sub-blocks of 256 (named barriers).  The round's leaves are cut into tiles of WPW * 256 rows;
-// CTA x takes a contiguous range of the tile list (so it meets few leaves), its sub-blocks take the tiles of a leaf in turn.
-// A tile: PartitionTiles' steps (entries -> bins -> ballots -> one cursor atomic per tile -> scatter); rows of the chosen side
-// are appended to a per-warp list in shared memory, and the warp then runs HistRows' pipelined update loop over the full
-// 32-row groups of its list (the remainder waits for the next tile; a predicated tail runs before each flush).  The shared
-// histograms are flushed when the CTA moves to another leaf and before a 16-bit lane could overflow.  With several feature
-// tiles (F > features per CTA) the CTAs of the other feature tiles repeat the side decision but not the scatter.
-constexpr int kExpandSubs = kHistThreads / kPartThreads;      // 4
-
-template <bool FLT> struct ListEntry { int row; unsigned pk; };
-template <> struct ListEntry<true> { int row; unsigned gx, hx; int pad_; };
-
-template <int R, int BPL, bool FLT>
-__device__ __forceinline__ void ExpandHistGroups(const ListEntry<FLT>* list, int ng, const uint8_t* rmc, unsigned rm_stride, unsigned lane_addr) {
-  constexpr int LPR = 32 / R;
-  constexpr int STEPS = 32 / R;
-  constexpr int U = 8;
-  constexpr int NU = STEPS / U;
-  const int lane = threadIdx.x & 31;
-  const int r = lane / LPR;
-  if (ng <= 0) return;
-  auto load_bins = [&](int row_l, int unit, unsigned (&bb)[U]) {
-    #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const unsigned row = static_cast<unsigned>(__shfl_sync(0xffffffffu, row_l, (unit * U + u) * R + r));
-      const uint8_t* src = rmc + static_cast<size_t>(row) * rm_stride;
-      if (BPL == 4) bb[u] = __ldg(reinterpret_cast<const unsigned int*>(src));
-      else bb[u] = __ldg(reinterpret_cast<const unsigned short*>(src));
-    }
-  };
-  ListEntry<FLT> cur = list[lane];
-  unsigned b_cur[U];
-  load_bins(cur.row, 0, b_cur);
-  #pragma unroll 1
-  for (int j = 0; j < ng; ++j) {
-    ListEntry<FLT> nxt = cur;
-    if (j + 1 < ng) nxt = list[(j + 1) * 32 + lane];
-    #pragma unroll
-    for (int unit = 0; unit < NU; ++unit) {
-      unsigned b_nxt[U];
-      if (unit + 1 < NU) {
-        load_bins(cur.row, unit + 1, b_nxt);
-      } else if (j + 1 < ng) {
-        load_bins(nxt.row, 0, b_nxt);
-      } else {
-        #pragma unroll
-        for (int u = 0; u < U; ++u) b_nxt[u] = 0;
-      }
-      #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int srcl = (unit * U + u) * R + r;
-        unsigned pk = 0, gx = 0, hx = 0;
-        if constexpr (FLT) { gx = __shfl_sync(0xffffffffu, cur.gx, srcl); hx = __shfl_sync(0xffffffffu, cur.hx, srcl); }
-        else pk = __shfl_sync(0xffffffffu, cur.pk, srcl);
-        HistUpdate<BPL, FLT>(b_cur[u], lane_addr, pk, gx, hx);
-      }
-      #pragma unroll
-      for (int u = 0; u < U; ++u) b_cur[u] = b_nxt[u];
-    }
-    cur = nxt;
-  }
-}
-
-// the last n < 32 rows of a warp's list: per-row predicates
-template <int R, int BPL, bool FLT>
-__device__ __forceinline__ void ExpandHistTail(const ListEntry<FLT>* list, int n, const uint8_t* rmc, unsigned rm_stride, unsigned lane_addr, bool kmask) {
-  constexpr int LPR = 32 / R;
-  constexpr int STEPS = 32 / R;
-  const int lane = threadIdx.x & 31;
-  const int r = lane / LPR;
-  if (n <= 0) return;
-  ListEntry<FLT> e;
-  e.row = -1;
-  if constexpr (FLT) { e.gx = 0; e.hx = 0; } else e.pk = 0;
-  if (lane < n) e = list[lane];
-  #pragma unroll 1
-  for (int s = 0; s * R < n; ++s) {
-    const int srcl = s * R + r;
-    const int row = __shfl_sync(0xffffffffu, e.row, srcl);
-    unsigned pk = 0, gx = 0, hx = 0;
-    if constexpr (FLT) { gx = __shfl_sync(0xffffffffu, e.gx, srcl); hx = __shfl_sync(0xffffffffu, e.hx, srcl); }
-    else pk = __shfl_sync(0xffffffffu, e.pk, srcl);
-    if (row >= 0 && kmask) {
-      const uint8_t* src = rmc + static_cast<size_t>(static_cast<unsigned>(row)) * rm_stride;
-      unsigned bb;
-      if (BPL == 4) bb = __ldg(reinterpret_cast<const unsigned int*>(src));
-      else bb = __ldg(reinterpret_cast<const unsigned short*>(src));
-      HistUpdate<BPL, FLT>(bb, lane_addr, pk, gx, hx);
-    }
-  }
-}
-
-struct ExpandShared {
-  int tiles[kMaxBatch + 1];        // first tile of every batch item in the round's tile list
-  int left_small[kMaxBatch];       // 1: the left child's histogram is built, 0: the right child's
-  int build[kMaxBatch];            // 0: the children are never searched, no histogram
-  unsigned long long rows;         // rows that went into histograms (statistics)
-  int wl[kExpandSubs][kPartThreads / 32], wr[kExpandSubs][kPartThreads / 32];
-  unsigned long long base[kExpandSubs];
-  int is_last;
-};
-
-template <int R, int BPL, bool FLT>
-__global__ void __launch_bounds__(kHistThreads, 1)
-k_bt_expand(const uint8_t* __restrict__ cm, long long n_pad, const uint8_t* __restrict__ rm, unsigned rm_stride,
-            const uint16_t* __restrict__ gh16, const int2* __restrict__ ghfix, int* idx0, int* idx1, BatchCtrl* __restrict__ ctrl,
-            long long* __restrict__ work, int work_elems, int F, int rows_per_flush, LearnerParams P, PeerTable pt) {
-  constexpr int LPR = 32 / R;
-  constexpr int FT = LPR * BPL;
-  constexpr int ES = FLT ? 4 : 2;
-  constexpr int WPW = FLT ? 2 : 4;                       // 32-row words per warp and tile
-  constexpr int NW = kPartThreads / 32;                  // warps per sub-block
-  constexpr int kTileRows = WPW * 32 * NW;               // 1024 (quantized) / 512 (float)
-  constexpr int kListCap = WPW * 32 + 32;                // a tile's rows + the carried remainder
-  extern __shared__ unsigned int hsm_raw[];
-  __shared__ ExpandShared sh;
-  PdlLaunchDependents();
-  const unsigned raw_addr = static_cast<unsigned>(__cvta_generic_to_shared(hsm_raw));
-  const unsigned sbase = (raw_addr + kHistArrayBytes - 1) & ~(kHistArrayBytes - 1);
-  unsigned int* hsm = hsm_raw + ((sbase - raw_addr) >> 2);
-  const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
-  const unsigned lane_addr = sbase + lane * 4;
-  // the per-warp row lists sit behind the four histogram arrays
-  ListEntry<FLT>* list = reinterpret_cast<ListEntry<FLT>*>(hsm + 4 * kBins * 32) + warp_in_cta * kListCap;
-  for (int i = threadIdx.x; i < 4 * kBins * 32; i += blockDim.x) hsm[i] = 0u;      // before the wait: overlaps the predecessor
-  const int ftile = blockIdx.y;
-  const int q = lane % LPR;
-  const bool kmask = (ftile * FT + q * BPL) < F;
-  const uint8_t* rmc = rm + static_cast<size_t>(ftile) * FT + (kmask ? q : 0) * BPL;
-  asm volatile("" : "+l"(rmc));
-  LGB_TRACE(ctrl, 10);
-  PdlWait();
-  LGB_TRACE(ctrl, 11);
-  if (Finished(ctrl)) return;
-  const int bn = ctrl->batch_n;
-  if (threadIdx.x < kMaxBatch) {
-    const int k = threadIdx.x;
-    int nt = 0, ls = 0, build = 0;
-    if (k < bn) {
-      const BatchItem& it = ctrl->batch[k];
-      nt = max(1, (it.src_count + kTileRows - 1) / kTileRows);
-      ls = it.est_left < it.est_right;
-      // children that will not be searched need no histogram; the serial learner decides that on true counts, known only after
-      // the partition, so there only the depth limit is used here (a histogram nobody reads is harmless)
-      build = it.search != 0 && !(P.dp && it.est_right < P.min_data_in_leaf * 2 && it.est_left < P.min_data_in_leaf * 2);
-    }
-    sh.tiles[k + 1] = nt; sh.left_small[k] = ls; sh.build[k] = build;
-  }
-  if (threadIdx.x == 0) { sh.tiles[0] = 0; sh.rows = 0ULL; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int t = 0, nb = 0;
-    for (int k = 0; k < kMaxBatch; ++k) { const int nt = sh.tiles[k + 1]; sh.tiles[k] = t; t += nt; nb += sh.build[k]; }
-    sh.tiles[kMaxBatch] = t;
-    if (blockIdx.x == 0 && ftile == 0) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_launches), static_cast<unsigned long long>(nb));
-  }
-  __syncthreads();
-  const int T = sh.tiles[kMaxBatch];
-  const int lo_tile = static_cast<int>(static_cast<long long>(T) * blockIdx.x / gridDim.x);
-  const int hi_tile = static_cast<int>(static_cast<long long>(T) * (blockIdx.x + 1) / gridDim.x);
-  const int sub = threadIdx.x >> 8;
-  const int t = threadIdx.x & (kPartThreads - 1);
-  const int warp = t >> 5;
-  const bool do_scatter = ftile == 0;
-  const int tiles_per_flush = max(1, rows_per_flush / kTileRows);
-  int list_n = 0;                       // rows waiting in this warp's list (warp-uniform)
-  unsigned long long my_rows = 0;
-  int k = 0;
-  for (int seg_lo = lo_tile; seg_lo < hi_tile;) {
-    while (k + 1 < kMaxBatch && seg_lo >= sh.tiles[k + 1]) ++k;
-    const int seg_hi = min(min(hi_tile, sh.tiles[k + 1]), seg_lo + tiles_per_flush);
-    const BatchItem& it = ctrl->batch[k];
-    const int n = it.src_count, begin = it.src_begin, buf = it.src_buf;
-    const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left;
-    const uint8_t* col = cm + static_cast<size_t>(it.feature) * n_pad;
-    const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0 : idx1);
-    const unsigned int* bag = buf < 0 ? ctrl->bag_bits : nullptr;
-    int* dst = (buf < 0 ? 0 : 1 - buf) == 0 ? idx0 : idx1;
-    const bool left_small = sh.left_small[k] != 0;
-    const bool build = sh.build[k] != 0;
-    for (int tile = seg_lo + sub; tile < seg_hi; tile += kExpandSubs) {
-      const int p_base = (tile - sh.tiles[k]) * kTileRows + warp * (WPW * 32) + lane;
-      int4 ent[WPW];
-      #pragma unroll
-      for (int u = 0; u < WPW; ++u) {
-        const int p = p_base + u * 32;
-        ent[u] = make_int4(-1, 0, 0, 0);
-        if (p < n) {
-          if (idx) {
-            if (ES == 2) { const int2 e = reinterpret_cast<const int2*>(idx)[begin + p]; ent[u].x = e.x; ent[u].y = e.y; }
-            else ent[u] = reinterpret_cast<const int4*>(idx)[begin + p];
-          } else if (bag == nullptr || ((bag[(begin + p) >> 5] >> ((begin + p) & 31)) & 1u)) {
-            const int row = begin + p;       // the root: rows are 0..n-1 (those in the bag), gradients come from the per-row arrays
-            ent[u].x = row;
-            if (ES == 2) {
-              const unsigned int g = gh16[row];
-              ent[u].y = static_cast<int>((static_cast<unsigned>(static_cast<int>(static_cast<signed char>(g >> 8))) << 16) + (g & 0xffu));
-            } else { const int2 g = ghfix[row]; ent[u].y = g.x; ent[u].z = g.y; }
-          }
-        }
-      }
-      int bins[WPW];
-      #pragma unroll
-      for (int u = 0; u < WPW; ++u) bins[u] = ent[u].x >= 0 ? col[ent[u].x] : -1;
-      unsigned int lmask[WPW], rmask[WPW];
-      int wl = 0, wr = 0;
-      #pragma unroll
-      for (int u = 0; u < WPW; ++u) {
-        const bool valid = ent[u].x >= 0;
-        const bool left = valid && ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr));
-        lmask[u] = __ballot_sync(0xffffffffu, left);
-        rmask[u] = __ballot_sync(0xffffffffu, valid && !left);
-        wl += __popc(lmask[u]); wr += __popc(rmask[u]);
-      }
-      const unsigned lt = (1u << lane) - 1u;
-      if (build) {       // rows of the chosen side join this warp's list
-        #pragma unroll
-        for (int u = 0; u < WPW; ++u) {
-          const unsigned sm = left_small ? lmask[u] : rmask[u];
-          if ((sm >> lane) & 1u) {
-            ListEntry<FLT>& e = list[list_n + __popc(sm & lt)];
-            e.row = ent[u].x;
-            if constexpr (FLT) { e.gx = static_cast<unsigned>(ent[u].y); e.hx = static_cast<unsigned>(ent[u].z); }
-            else e.pk = static_cast<unsigned>(ent[u].y);
-          }
-          list_n += __popc(sm);
-        }
-      }
-      if (do_scatter) {
-        if (lane == 0) { sh.wl[sub][warp] = wl; sh.wr[sub][warp] = wr; }
-        SubSync(sub);
-        int lefts_before = 0, rights_before = 0, tile_l = 0, tile_r = 0;
-        #pragma unroll
-        for (int w = 0; w < NW; ++w) {
-          const int a = sh.wl[sub][w], v = sh.wr[sub][w];
-          if (w < warp) { lefts_before += a; rights_before += v; }
-          tile_l += a; tile_r += v;
-        }
-        if (t == 0)
-          sh.base[sub] = atomicAdd(&ctrl->part_cursor[k], (static_cast<unsigned long long>(tile_l) << 32) | static_cast<unsigned>(tile_r));
-        SubSync(sub);
-        const unsigned long long base = sh.base[sub];
-        const int lbase = static_cast<int>(base >> 32), rbase = static_cast<int>(base & 0xffffffffu);
-        int lpos = begin + lbase + lefts_before;
-        int rpos = begin + n - rbase - tile_r + rights_before;
-        #pragma unroll
-        for (int u = 0; u < WPW; ++u) {
-          if (ent[u].x >= 0) {
-            const bool left = (lmask[u] >> lane) & 1u;
-            const int pos = left ? lpos + __popc(lmask[u] & lt) : rpos + __popc(rmask[u] & lt);
-            if (ES == 2) reinterpret_cast<int2*>(dst)[pos] = make_int2(ent[u].x, ent[u].y);
-            else reinterpret_cast<int4*>(dst)[pos] = ent[u];
-          }
-          lpos += __popc(lmask[u]);
-          rpos += __popc(rmask[u]);
-        }
-        SubSync(sub);      // sh.wl / sh.wr / sh.base are rewritten by the sub-block's next tile
-      }
-      // the histogram updates of the full 32-row groups of the warp's list (the entries and masks above are dead by now: the
-      // update loop needs the registers); other warps' tiles overlap it
-      if (build) {
-        __syncwarp();
-        const int ng = list_n >> 5;
-        ExpandHistGroups<R, BPL, FLT>(list, ng, rmc, rm_stride, lane_addr);
-        my_rows += static_cast<unsigned long long>(ng) * 32;
-        const int rem = list_n & 31;
-        ListEntry<FLT> carry;
-        if (ng > 0 && lane < rem) carry = list[ng * 32 + lane];
-        __syncwarp();
-        if (ng > 0 && lane < rem) list[lane] = carry;
-        list_n = rem;
-      }
-    }
-    // end of the segment: what is left in the lists, then the flush
-    if (build) {
-      __syncwarp();
-      ExpandHistTail<R, BPL, FLT>(list, list_n, rmc, rm_stride, lane_addr, kmask);
-      my_rows += list_n;
-      list_n = 0;
-    }
-    __syncthreads();
-    if (build) HistFlush<R, BPL, FLT, !FLT>(hsm, work + static_cast<size_t>(k) * work_elems, F, ftile);
-    __syncthreads();
-    seg_lo = seg_hi;
-  }
-  if (ftile == 0) {
-    if (lane == 0 && my_rows) atomicAdd(&sh.rows, my_rows);
-    __syncthreads();
-    if (threadIdx.x == 0 && sh.rows) atomicAdd(reinterpret_cast<unsigned long long*>(&ctrl->hist_rows), sh.rows);
-  }
-  if (pt.world > 0) {      // the CTA that finishes last tells the other ranks that this rank's histograms are complete
-    __threadfence();
-    __syncthreads();
-    PeerMail* me = pt.mail[pt.rank];
-    if (threadIdx.x == 0) {
-      const bool last = atomicAdd(&me->hist_count, 1u) == gridDim.x * gridDim.y - 1;
-      if (last) me->hist_count = 0u;
-      sh.is_last = last;
-    }
-    __syncthreads();
-    if (sh.is_last && threadIdx.x < pt.world) {
-      __threadfence_system();
-      StoreReleaseSys(&pt.mail[threadIdx.x]->hist_flag[pt.rank], pt.seq);
-    }
-  }
   LGB_TRACE(ctrl, 12);
 }
 

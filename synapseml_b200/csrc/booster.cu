@@ -107,9 +107,6 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
   // search's last unit does, as for wide data)
   lp_.reduce_in_select = F_ <= 32 && !(getenv("LGB_B200_REDUCE_IN_SELECT") && atoi(getenv("LGB_B200_REDUCE_IN_SELECT")) == 0);
-  // partition + histogram of the chosen child in one kernel (batch_tree.cuh: k_bt_expand); LGB_B200_FUSED=0: two kernels
-  fused_ = !(getenv("LGB_B200_FUSED") && atoi(getenv("LGB_B200_FUSED")) == 0);
-  lp_.fused = fused_ ? 1 : 0;
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -118,10 +115,16 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   }
 
   const int L = cfg_.num_leaves;
-  d_score_.AllocZero(n_);
-  if (train->has_init_score) LGB_CUDA(cudaMemcpy(d_score_.p, train->d_init_score.p, sizeof(double) * n_, cudaMemcpyDeviceToDevice));
-  d_grad_[0].Alloc(n_); d_hess_[0].Alloc(n_); d_grad_[1].Alloc(n_); d_hess_[1].Alloc(n_);
-  if (const char* env = getenv("LGB_B200_FUSE_GRAD")) fuse_grad_ = atoi(env) != 0;
+  d_score_.AllocZero(n_ * K_);      // class-major [K_][n_]
+  if (train->has_init_score) {
+    LGB_CHECK(static_cast<int64_t>(train->init_score.size()) == n_ * K_, "init_score holds %lld values, expected num_data * num_class = %lld",
+              static_cast<long long>(train->init_score.size()), static_cast<long long>(n_ * K_));
+    LGB_CUDA(cudaMemcpy(d_score_.p, train->d_init_score.p, sizeof(double) * n_ * K_, cudaMemcpyDeviceToDevice));
+  }
+  d_grad_[0].Alloc(n_ * K_); d_hess_[0].Alloc(n_ * K_);
+  d_grad_[1].Alloc(K_ == 1 ? n_ : 1); d_hess_[1].Alloc(K_ == 1 ? n_ : 1);      // the second pair only serves the fused apply + gradient pass
+  if (K_ > 1) fuse_grad_ = false;      // a row's gradients depend on all K scores: one gradient kernel per iteration
+  if (const char* env = getenv("LGB_B200_FUSE_GRAD")) fuse_grad_ = atoi(env) != 0 && K_ == 1;
   if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
   idx_es_ = lp_.quantized ? 2 : 4;      // ints per index entry: {row, g|h} or {row, g, h, -}
   d_idx_[0].Alloc(n_ * idx_es_); d_idx_[1].Alloc(n_ * idx_es_);
@@ -194,10 +197,6 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   SET_HIST_SMEM(4, 4, false); SET_HIST_SMEM(2, 4, false); SET_HIST_SMEM(1, 4, false);
   SET_HIST_SMEM(4, 2, true); SET_HIST_SMEM(2, 2, true); SET_HIST_SMEM(1, 2, true);
 #undef SET_HIST_SMEM
-  // the fused kernel keeps a row list per warp behind the histograms: (tile rows + 32) entries of 8 (quantized) / 16 (float) bytes
-  expand_smem_ = kHistSmem + (kHistThreads / 32) * (lp_.quantized ? (4 * 32 + 32) * 8 : (2 * 32 + 32) * 16);
-  SetSmem(k_bt_expand<4, 4, false>, expand_smem_); SetSmem(k_bt_expand<2, 4, false>, expand_smem_); SetSmem(k_bt_expand<1, 4, false>, expand_smem_);
-  SetSmem(k_bt_expand<4, 2, true>, expand_smem_); SetSmem(k_bt_expand<2, 2, true>, expand_smem_); SetSmem(k_bt_expand<1, 2, true>, expand_smem_);
   LGB_CUDA(cudaStreamSynchronize(stream_));
   prof_ = getenv("LGB_B200_PROFILE") != nullptr;
 }
@@ -342,6 +341,7 @@ void Booster::ResetParameter(const char* params) {
 // ---------------------------------------------------------------------------------------------------- objectives
 void Booster::InitObjective() {
   const std::vector<float>& label = ds_->label;
+  const double kEpsD = 1e-15f;
   if (cfg_.objective == "binary") {
     obj_ = kBinary;
     double cnt[2] = {0.0, 0.0};
@@ -426,10 +426,30 @@ void Booster::InitObjective() {
       LGB_CHECK(acc[0] == 0.0, "objective=%s needs %s labels", o.c_str(), obj_ == kGamma ? "positive" : "non-negative");
       LGB_CHECK(acc[1] > 0.0, "objective=%s: the sum of the labels is zero", o.c_str());
     }
+  } else if (cfg_.objective == "multiclass") {
+    // MulticlassSoftmax::Init (upstream multiclass_objective.hpp): label shares over all machines, classes that never / always occur
+    obj_ = kMulticlass;
+    K_ = cfg_.num_class;
+    LGB_CHECK(K_ >= 2 && K_ <= kMaxClasses, "objective=multiclass needs 2 <= num_class <= %d (got %d)", kMaxClasses, K_);
+    std::vector<double> acc(K_ + 1, 0.0);      // [K_] = sum of weights
+    const std::vector<float>& wv = ds_->weight;
+    for (int64_t i = 0; i < n_; ++i) {
+      const int l = static_cast<int>(label[i]);
+      LGB_CHECK(l >= 0 && l < K_ && label[i] == static_cast<float>(l), "multiclass labels must be integers in [0, %d)", K_);
+      const double w = has_weights_ ? wv[i] : 1.0;
+      acc[l] += w; acc[K_] += w;
+    }
+    net_->HostAllReduceSum(acc.data(), K_ + 1);
+    class_init_probs_.assign(K_, 0.0);
+    class_need_train_.assign(K_, 1);
+    for (int k = 0; k < K_; ++k) {
+      class_init_probs_[k] = acc[k] / acc[K_];
+      if (std::fabs(class_init_probs_[k]) <= kEpsD || std::fabs(class_init_probs_[k]) >= 1.0 - kEpsD) class_need_train_[k] = 0;
+    }
   } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
     obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, regression, lambdarank, custom)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, regression, lambdarank, custom)");
   }
 }
 
@@ -452,7 +472,9 @@ void Booster::ComputeGradients() {
   const int n = static_cast<int>(n_);
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
   const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
-  if (obj_ == kBinary) {
+  if (obj_ == kMulticlass) {
+    k_grad_multiclass<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[0].p, d_hess_[0].p, n, K_, static_cast<double>(K_) / (K_ - 1.0f));
+  } else if (obj_ == kBinary) {
     k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
     k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
@@ -490,12 +512,14 @@ void Booster::PrepareGradients(bool absmax_ready) {
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
   if (!absmax_ready) {
     LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
-    k_absmax<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, d_ctrl_);
+    k_absmax<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p + cls_ * n_, d_hess_[grad_cur_].p + cls_ * n_, n, d_ctrl_);
   }
   if (peers_.world > 0) { k_peer_max<<<1, 32, 0, stream_>>>(d_ctrl_, peers_, ++max_seq_); ++launches_; }
   else if (nccl_exchange_) net_->AllReduceMaxU32(&d_ctrl_->max_abs_g_bits, 2, stream_);
   k_scales<<<1, 1, 0, stream_>>>(d_ctrl_, lp_);
-  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_, static_cast<unsigned int>(iter_),
+  // the stochastic-rounding stream is keyed by the tree (iteration * K + class) and the global row
+  k_quantize<<<grid, 256, 0, stream_>>>(d_grad_[grad_cur_].p + cls_ * n_, d_hess_[grad_cur_].p + cls_ * n_, n, static_cast<const BatchCtrl*>(d_ctrl_), lp_,
+                                        static_cast<unsigned int>(iter_ * K_ + cls_),
                                         static_cast<unsigned int>(row_offset_), d_gh16_.p, d_ghfix_.p,
                                         bagging_ ? d_bag_bits_.p : nullptr);
   LGB_CUDA(cudaGetLastError());
@@ -529,13 +553,13 @@ void Booster::LaunchHist(bool root) {
   if (root) LGB_CUDA(cudaMemsetAsync(work, 0, sizeof(long long) * work_elems_, stream_));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (time_hist_) {
-    if (hist_events_used_ == hist_events_.size()) {
+    if (hist_events_total_ == hist_events_.size()) {
       cudaEvent_t a, b;
       LGB_CUDA(cudaEventCreate(&a)); LGB_CUDA(cudaEventCreate(&b));
       hist_events_.emplace_back(a, b);
     }
-    e0 = hist_events_[hist_events_used_].first; e1 = hist_events_[hist_events_used_].second;
-    ++hist_events_used_;
+    e0 = hist_events_[hist_events_total_].first; e1 = hist_events_[hist_events_total_].second;
+    ++hist_events_total_;
     LGB_CUDA(cudaEventRecord(e0, stream_));
   }
 #define LAUNCH_HIST_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, d_idx_[0].p, d_idx_[1].p, \
@@ -568,14 +592,12 @@ void Booster::LaunchFind(bool root) {
   pt.seq = exchange_seq_;
   pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
   long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
-  long long* clear = fused_ ? d_hist_work_.p + ((exchange_seq_ + 1u) & 1u) * work_stride_ : nullptr;
-  const long long clear_elems = static_cast<long long>(work_elems_) * max_batch_;
   if (lp_.quantized)
     LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt, clear, clear_elems);
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   else
     LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt, clear, clear_elems);
+              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   ++launches_;
 }
 
@@ -596,76 +618,21 @@ void Booster::LaunchSelect(bool after_root) {
 // and returns at once when the tree is finished, so rounds are enqueued without waiting for the GPU.
 void Booster::EnqueueRounds(int rounds) {
   for (int r = 0; r < rounds; ++r) {
-    if (fused_) {
-      ProfBegin("expand"); LaunchExpand(); ProfEnd();
-    } else {
-      ProfBegin("partition");
-      // the partition kernel clears the work areas the round's histograms go into
-      long long* next_work = d_hist_work_.p + ((exchange_seq_ + 1u) & 1u) * work_stride_;
-      if (idx_es_ == 2)
-        LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                  d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
-      else
-        LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
-                  d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
-      ProfEnd();
-      ProfBegin("hist"); LaunchHist(false); ProfEnd();
-      launches_ += 1;
-    }
+    ProfBegin("partition");
+    // the partition kernel clears the work areas the round's histograms go into
+    long long* next_work = d_hist_work_.p + ((exchange_seq_ + 1u) & 1u) * work_stride_;
+    if (idx_es_ == 2)
+      LaunchPdl(k_bt_partition<2>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
+    else
+      LaunchPdl(k_bt_partition<4>, dim3(part_blocks_), dim3(kPartThreads), 0, stream_, ds_->d_cm.p, static_cast<long long>(ds_->n_pad),
+                d_idx_[0].p, d_idx_[1].p, d_idx_[0].p, d_idx_[1].p, d_gh16_.p, d_ghfix_.p, d_ctrl_, next_work, work_elems_);
+    ProfEnd();
+    ProfBegin("hist"); LaunchHist(false); ProfEnd();
+    launches_ += 1;
     ProfBegin("find"); LaunchFind(false); ProfEnd();
     LaunchSelect(false);
   }
-}
-
-// Partition + histogram of the chosen child for every leaf of the batch (k_bt_expand).
-void Booster::LaunchExpand() {
-  const BinLayout& lay = ds_->layout;
-  const int R = lay.rows_per_step;
-  const bool flt = !lp_.quantized;
-  const int ft = flt ? lay.tile_features_f : lay.tile_features_q;
-  const int tiles = CeilDiv(F_, ft);
-  const int row_ctas = std::max(1, kNumSms / tiles);
-  dim3 grid(row_ctas, tiles);
-  int rows_per_flush;
-  if (flt) {
-    rows_per_flush = kFixRowsPerCopy * R;
-  } else {
-    const int qb = cfg_.num_grad_quant_bins;
-    const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
-    rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
-  }
-  PeerTable pt = peers_;
-  ++exchange_seq_;
-  pt.seq = exchange_seq_;
-  long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (time_hist_) {
-    if (hist_events_used_ == hist_events_.size()) {
-      cudaEvent_t a, b;
-      LGB_CUDA(cudaEventCreate(&a)); LGB_CUDA(cudaEventCreate(&b));
-      hist_events_.emplace_back(a, b);
-    }
-    e0 = hist_events_[hist_events_used_].first; e1 = hist_events_[hist_events_used_].second;
-    ++hist_events_used_;
-    LGB_CUDA(cudaEventRecord(e0, stream_));
-  }
-#define EXPAND_ARGS ds_->d_cm.p, static_cast<long long>(ds_->n_pad), ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_gh16_.p, d_ghfix_.p, \
-                    d_idx_[0].p, d_idx_[1].p, d_ctrl_, work, work_elems_, F_, rows_per_flush, lp_, pt
-  if (!flt) {
-    if (R == 4) LaunchPdl(k_bt_expand<4, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-    else if (R == 2) LaunchPdl(k_bt_expand<2, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-    else LaunchPdl(k_bt_expand<1, 4, false>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-  } else {
-    if (R == 4) LaunchPdl(k_bt_expand<4, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-    else if (R == 2) LaunchPdl(k_bt_expand<2, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-    else LaunchPdl(k_bt_expand<1, 2, true>, grid, dim3(kHistThreads), expand_smem_, stream_, EXPAND_ARGS);
-  }
-#undef EXPAND_ARGS
-  LGB_CUDA(cudaGetLastError());
-  if (time_hist_) LGB_CUDA(cudaEventRecord(e1, stream_));
-  ++launches_;
-  ++hist_kernel_launches_;
-  if (nccl_exchange_) net_->AllReduceSumInt64(work, static_cast<size_t>(work_elems_) * max_batch_, stream_);
 }
 
 // ColSampler::ResetByTree (upstream src/treelearner/col_sampler.hpp): every tree draws max(round(F * feature_fraction), min(2, F))
@@ -701,7 +668,6 @@ void Booster::SampleFeaturesForTree() {
 void Booster::TrainTree(HostTree* out) {
   const int L = cfg_.num_leaves;
   const int n = static_cast<int>(n_);
-  hist_events_used_ = 0;
   if (trace_cap_ > 0) {      // trace three trees starting at iteration LGB_B200_TRACE_FROM
     long long* p = (iter_ >= trace_from_ && iter_ < trace_from_ + 3) ? d_trace_.p : nullptr;
     LGB_CUDA(cudaMemcpyAsync(&d_ctrl_->trace, &p, sizeof(p), cudaMemcpyHostToDevice, stream_));
@@ -807,7 +773,7 @@ void Booster::UpdateScores() {
   float* g = d_grad_[grad_cur_ ^ 1].p;
   float* h = d_hess_[grad_cur_ ^ 1].p;
   if (obj != 0) LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
-#define APPLY_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_score_.p, ds_->d_label.p, w, g, h, tree_dev_, ds_->d_fmeta.p, d_ctrl_, \
+#define APPLY_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_score_.p + cls_ * n_, ds_->d_label.p, w, g, h, tree_dev_, ds_->d_fmeta.p, d_ctrl_, \
                    cfg_.learning_rate, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]
 #define APPLY(OBJ)                                                                                              \
   do {                                                                                                          \
@@ -833,7 +799,7 @@ void Booster::ApplyTreeToValidSets() {
     if (n == 0) continue;
     const BinLayout& lay = d->layout;
     const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
-#define APPLY_V(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p, \
+#define APPLY_V(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p + cls_ * d->num_data, \
         nullptr, nullptr, nullptr, nullptr, tree_dev_, ds_->d_fmeta.p, d_ctrl_, cfg_.learning_rate, n, cfg_.sigmoid, 1.0, 1.0)
     if (lay.rm_stride == 32) APPLY_V(8); else if (lay.rm_stride == 64) APPLY_V(16); else APPLY_V(0);
 #undef APPLY_V
@@ -845,7 +811,7 @@ void Booster::AddConstantToValidSets(double v) {
   for (ValidSet& s : valids_) {
     const int n = static_cast<int>(s.ds->num_data);
     if (n == 0) continue;
-    k_add_constant<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(s.score.p, n, v);
+    k_add_constant<<<std::min(CeilDiv(n, 256), kNumSms * 8), 256, 0, stream_>>>(s.score.p + cls_ * s.ds->num_data, n, v);
     ++launches_;
   }
 }
@@ -867,24 +833,28 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   LGB_CHECK(!predict_only_, "this booster was loaded from a model string and can only predict");
   LGB_CUDA(cudaSetDevice(device_));
   const double kEps = 1e-15f;
-  double init_score = 0.0;
   const bool custom = custom_grad != nullptr;
+  LGB_CHECK(!(custom && K_ > 1), "LGBM_BoosterUpdateOneIterCustom with multiclass is not supported by this library yet");
   // ObtainAutomaticInitialScore (upstream src/boosting/gbdt.cpp): the objective's BoostFromScore over the labels of all machines,
   // then the mean over machines of what are identical values
   auto automatic_init_score = [&]() -> double {
     if (obj_ == kLambdarank || obj_ == kCustom) return 0.0;
-    double sums[2];
-    BoostFromScoreLocalSums(&sums[0], &sums[1]);
-    net_->HostAllReduceSum(sums, 2);
     double v;
-    if (obj_ == kBinary) {
-      double pavg = sums[0] / sums[1];
-      pavg = std::min(pavg, 1.0 - kEps);
-      pavg = std::max<double>(pavg, kEps);
-      v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
+    if (obj_ == kMulticlass) {
+      v = std::log(std::max<double>(kEps, class_init_probs_[cls_]));
     } else {
-      v = sums[0] / sums[1];
-      if (LogLink()) v = v > 0.0 ? std::log(v) : -std::numeric_limits<double>::infinity();      // Common::SafeLog of the mean label
+      double sums[2];
+      BoostFromScoreLocalSums(&sums[0], &sums[1]);
+      net_->HostAllReduceSum(sums, 2);
+      if (obj_ == kBinary) {
+        double pavg = sums[0] / sums[1];
+        pavg = std::min(pavg, 1.0 - kEps);
+        pavg = std::max<double>(pavg, kEps);
+        v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
+      } else {
+        v = sums[0] / sums[1];
+        if (LogLink()) v = v > 0.0 ? std::log(v) : -std::numeric_limits<double>::infinity();      // Common::SafeLog of the mean label
+      }
     }
     if (net_->active()) {
       double acc = 0.0;
@@ -893,25 +863,28 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     }
     return v;
   };
-  auto add_to_scores = [&](double v) {
-    k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p, static_cast<int>(n_), v);
+  auto add_to_scores = [&](double v) {      // to the scores of class cls_
+    k_add_constant<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(d_score_.p + cls_ * n_, static_cast<int>(n_), v);
     AddConstantToValidSets(v);
     ++launches_;
   };
-  // GBDT::BoostFromAverage
+  // GBDT::BoostFromAverage, once per class
+  std::vector<double> init_scores(K_, 0.0);
   if (!custom && models_.empty() && !ds_->has_init_score && (cfg_.boost_from_average || F_ == 0)) {
-    const double v = automatic_init_score();
-    if (std::fabs(v) > kEps) {
-      init_score = v;
-      add_to_scores(v);
-      LogInfo("Start training from score %lf", v);
+    for (cls_ = 0; cls_ < K_; ++cls_) {
+      const double v = automatic_init_score();
+      if (std::fabs(v) > kEps) {
+        init_scores[cls_] = v;
+        add_to_scores(v);
+        LogInfo("Start training from score %lf", v);
+      }
     }
+    cls_ = 0;
   }
-  HostTree tree;
-  tree.num_leaves = 1;
-  tree.leaf_value.assign(1, 0.0);
-  if (need_train_ && F_ > 0) {
-    const bool fused = grad_ready_ && !custom;       // produced by the previous iteration's apply-tree pass
+  // Boosting(): the gradients of all classes from the scores before this iteration's trees
+  const bool any_train = K_ > 1 ? std::any_of(class_need_train_.begin(), class_need_train_.end(), [](char c) { return c != 0; }) : need_train_;
+  const bool fused = grad_ready_ && !custom;       // produced by the previous iteration's apply-tree pass
+  if (any_train && F_ > 0) {
     if (fused) grad_cur_ ^= 1;
     else if (custom) {       // pageable sources are staged before the calls return
       LGB_CUDA(cudaMemcpyAsync(d_grad_[grad_cur_].p, custom_grad, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
@@ -919,38 +892,48 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     } else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
     grad_ready_ = false;
     Bagging();
-    ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
-    TrainTree(&tree);
-    if (tree.num_leaves <= 1) grad_ready_ = false;      // no tree, so the apply pass did nothing
   }
   bool should_continue = false;
-  if (tree.num_leaves > 1) {
-    should_continue = true;      // (the scores were advanced inside TrainTree, behind the tree's last round)
-    tree.Shrinkage(cfg_.learning_rate);
-    if (std::fabs(init_score) > kEps) tree.AddBias(init_score);
-  } else if (models_.empty()) {
-    // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
-    // (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
-    if (!custom && obj_ != kCustom && !cfg_.boost_from_average && !ds_->has_init_score) {
-      init_score = automatic_init_score();
-      add_to_scores(init_score);
+  for (cls_ = 0; cls_ < K_; ++cls_) {
+    HostTree tree;
+    tree.num_leaves = 1;
+    tree.leaf_value.assign(1, 0.0);
+    const bool train_this = K_ > 1 ? class_need_train_[cls_] != 0 : need_train_;
+    if (train_this && F_ > 0) {
+      ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
+      TrainTree(&tree);
+      if (tree.num_leaves <= 1) grad_ready_ = false;      // no tree, so the apply pass did nothing
     }
-    tree.AsConstantTree(init_score);
+    if (tree.num_leaves > 1) {
+      should_continue = true;      // (the scores were advanced inside TrainTree, behind the tree's last round)
+      tree.Shrinkage(cfg_.learning_rate);
+      if (std::fabs(init_scores[cls_]) > kEps) tree.AddBias(init_scores[cls_]);
+    } else if (static_cast<int>(models_.size()) < K_) {
+      // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
+      // (above) and only names the constant tree; without it — and with an objective and no init_score — it is obtained here
+      if (!custom && obj_ != kCustom && !cfg_.boost_from_average && !ds_->has_init_score) {
+        init_scores[cls_] = automatic_init_score();
+        add_to_scores(init_scores[cls_]);
+      }
+      tree.AsConstantTree(init_scores[cls_]);
+    }
+    models_.push_back(std::move(tree));
   }
+  cls_ = 0;
   // per-iteration histogram timing (only when enabled by the bench / tests)
-  if (time_hist_ && hist_events_used_ > 0) {
+  if (time_hist_ && hist_events_total_ > 0) {
     Sync();
-    for (size_t i = 0; i < hist_events_used_; ++i) {
+    for (size_t i = 0; i < hist_events_total_; ++i) {
       float ms = 0;
       LGB_CUDA(cudaEventElapsedTime(&ms, hist_events_[i].first, hist_events_[i].second));
       last_hist_ms_ += ms;
     }
   }
-  models_.push_back(std::move(tree));
+  hist_events_total_ = 0;
   ++model_version_;
   if (!should_continue) {
     LogWarning("Stopped training because there are no more leaves that meet the split requirements");
-    if (models_.size() > 1) models_.pop_back();
+    if (static_cast<int>(models_.size()) > K_) for (int k = 0; k < K_; ++k) models_.pop_back();
     ++model_version_;
     Sync();
     return true;
@@ -965,6 +948,7 @@ ModelHeader Booster::MakeHeader() const {
   h.max_feature_idx = ds_->num_total_features - 1;
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
   else if (obj_ == kL2) h.objective = "regression";
+  else if (obj_ == kMulticlass) { h.objective = "multiclass num_class:" + std::to_string(K_); h.num_class = K_; h.num_tree_per_iteration = K_; }
   else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
   else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
@@ -984,14 +968,14 @@ std::string Booster::SaveModelToString(int start_iteration, int num_iteration) c
 void Booster::CopyScores(double* out) const {
   LGB_CUDA(cudaSetDevice(device_));
   Sync();
-  LGB_CUDA(cudaMemcpy(out, d_score_.p, sizeof(double) * n_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(out, d_score_.p, sizeof(double) * n_ * K_, cudaMemcpyDeviceToHost));      // class-major [K][n]
 }
 
 void Booster::CopyGradients(float* g, float* h) const {
   LGB_CUDA(cudaSetDevice(device_));
   Sync();
-  LGB_CUDA(cudaMemcpy(g, d_grad_[grad_cur_].p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
-  LGB_CUDA(cudaMemcpy(h, d_hess_[grad_cur_].p, sizeof(float) * n_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(g, d_grad_[grad_cur_].p, sizeof(float) * n_ * K_, cudaMemcpyDeviceToHost));
+  LGB_CUDA(cudaMemcpy(h, d_hess_[grad_cur_].p, sizeof(float) * n_ * K_, cudaMemcpyDeviceToHost));
 }
 
 void Booster::CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const {
@@ -1017,6 +1001,10 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
   } else if (o.rfind("lambdarank", 0) == 0) {
     obj_ = kLambdarank;
+  } else if (o.rfind("multiclass", 0) == 0 && o.rfind("multiclassova", 0) != 0) {
+    obj_ = kMulticlass;
+    K_ = loaded_header_.num_tree_per_iteration;
+    LGB_CHECK(K_ >= 2 && K_ == loaded_header_.num_class, "Model string: multiclass needs num_tree_per_iteration == num_class >= 2");
   } else if (o == "huber" || o == "fair" || o == "poisson" || o == "gamma" || o == "tweedie") {
     obj_ = o == "huber" ? kHuber : o == "fair" ? kFair : o == "poisson" ? kPoisson : o == "gamma" ? kGamma : kTweedie;
     cfg_.objective = o;
@@ -1027,8 +1015,12 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     obj_ = kL2;
   }
   for (auto& kv : loaded_header_.parameters) cfg_.raw[kv.first] = kv.second;
+  LGB_CHECK(loaded_header_.num_tree_per_iteration == K_ && loaded_header_.num_class == K_,
+            "Model string: num_class=%d / num_tree_per_iteration=%d do not fit objective '%s'", loaded_header_.num_class,
+            loaded_header_.num_tree_per_iteration, o.c_str());
+  LGB_CHECK(models_.size() % K_ == 0, "Model string: %d trees are not a multiple of num_tree_per_iteration", static_cast<int>(models_.size()));
   device_ = -1;      // resolved at the first prediction: loading and re-saving a model needs no GPU
-  iter_ = static_cast<int>(models_.size());
+  iter_ = static_cast<int>(models_.size()) / K_;
   model_version_ = 1;
 }
 
@@ -1036,8 +1028,9 @@ void Booster::MergeFrom(const Booster& other) {
   LGB_CHECK(!predict_only_, "LGBM_BoosterMerge: the receiving booster must be a training booster");
   LGB_CHECK(other.NumTotalFeatures() == NumTotalFeatures(), "LGBM_BoosterMerge: the merged model has %d features, the training data %d",
             other.NumTotalFeatures(), NumTotalFeatures());
+  LGB_CHECK(other.K_ == K_, "LGBM_BoosterMerge: the merged model has %d trees per iteration, this booster %d", other.K_, K_);
   std::vector<HostTree> merged(other.models_);
-  num_init_iteration_ = static_cast<int>(merged.size());
+  num_init_iteration_ = static_cast<int>(merged.size()) / K_;
   for (HostTree& t : models_) merged.push_back(std::move(t));
   models_ = std::move(merged);
   ++model_version_;
@@ -1049,7 +1042,7 @@ void Booster::FeatureImportance(int num_iteration, int importance_type, double* 
   LGB_CHECK(importance_type == 0 || importance_type == 1, "FeatureImportance: importance_type must be 0 (split) or 1 (gain)");
   const int nf = NumTotalFeatures();
   for (int j = 0; j < nf; ++j) out[j] = 0.0;
-  const int n = num_iteration > 0 ? std::min<int>(num_iteration, static_cast<int>(models_.size())) : static_cast<int>(models_.size());
+  const int n = num_iteration > 0 ? std::min<int>(num_iteration * K_, static_cast<int>(models_.size())) : static_cast<int>(models_.size());
   for (int t = 0; t < n; ++t) {
     const HostTree& tr = models_[t];
     for (int k = 0; k < tr.num_leaves - 1; ++k) {
@@ -1066,15 +1059,15 @@ std::string Booster::DumpModel(int start_iteration, int num_iteration, int impor
 }
 
 void Booster::TreeRange(int start_iteration, int num_iteration, int* t0, int* t1) const {
-  const int n = static_cast<int>(models_.size());
-  *t0 = std::min(std::max(0, start_iteration), n);
-  *t1 = num_iteration > 0 ? std::min(n, *t0 + num_iteration) : n;
+  const int n = static_cast<int>(models_.size());      // iterations -> trees (K_ per iteration)
+  *t0 = std::min(std::max(0, start_iteration) * K_, n);
+  *t1 = num_iteration > 0 ? std::min(n, *t0 + num_iteration * K_) : n;
 }
 
 int64_t Booster::CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const {
   int t0, t1;
   TreeRange(start_iteration, num_iteration, &t0, &t1);
-  return predict_type == kPredictLeaf ? nrow * (t1 - t0) : nrow;
+  return predict_type == kPredictLeaf ? nrow * (t1 - t0) : nrow * K_;
 }
 
 void Booster::UploadModel() {
@@ -1115,7 +1108,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   UploadModel();
   int t0, t1;
   TreeRange(start_iteration, num_iteration, &t0, &t1);
-  const int per_row = predict_type == kPredictLeaf ? (t1 - t0) : 1;
+  const int per_row = predict_type == kPredictLeaf ? (t1 - t0) : K_;
   if (out_len) *out_len = nrow * per_row;
   if (nrow == 0 || per_row == 0) return;
   PredModelDev m;
@@ -1126,7 +1119,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
   dp_in_.Reserve(static_cast<size_t>(chunk_rows) * ncol * esz);
   dp_out_.Reserve(static_cast<size_t>(chunk_rows) * per_row);
-  const int sig_on = obj_ == kBinary ? 1 : LogLink() ? 2 : 0;      // ConvertOutput: sigmoid, exp, or none
+  const int sig_on = obj_ == kBinary ? 1 : LogLink() ? 2 : obj_ == kMulticlass ? 3 : 0;      // ConvertOutput: sigmoid, exp, softmax or none
   for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
     const int64_t nr = std::min(chunk_rows, nrow - r0);
     const unsigned char* src = static_cast<const unsigned char*>(data) + (row_major ? static_cast<size_t>(r0) * ncol * esz : 0);
@@ -1134,10 +1127,10 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
     const long long rs = row_major ? ncol : 1, cs = row_major ? 1 : nr;
     const int grid = static_cast<int>(std::min<int64_t>(CeilDiv(static_cast<int>(std::min<int64_t>(nr, 1 << 30)), 128), kNumSms * 16));
     if (data_type == 1)
-      k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, predict_type, sig_on,
+      k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, predict_type, sig_on,
                                                    cfg_.sigmoid, dp_out_.p);
     else
-      k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, predict_type, sig_on,
+      k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, predict_type, sig_on,
                                                   cfg_.sigmoid, dp_out_.p);
     LGB_CUDA(cudaGetLastError());
     LGB_CUDA(cudaMemcpyAsync(out + static_cast<size_t>(r0) * per_row, dp_out_.p, sizeof(double) * nr * per_row, cudaMemcpyDeviceToHost, stream_));
@@ -1188,7 +1181,7 @@ float Booster::TimeRootHistogram(int repeats) {
   time_hist_ = true;
   float total = 0;
   for (int r = 0; r < repeats; ++r) {
-    hist_events_used_ = 0;
+    hist_events_total_ = 0;
     LaunchHist(true);
     Sync();
     float ms = 0;
@@ -1196,6 +1189,7 @@ float Booster::TimeRootHistogram(int repeats) {
     total += ms;
   }
   time_hist_ = was;
+  hist_events_total_ = 0;
   return total / repeats;
 }
 

@@ -95,7 +95,6 @@ struct LearnerParams {
   int min_data_in_leaf, max_depth, num_leaves, num_features;
   int quantized, dp, num_grad_quant_bins, stochastic_rounding, const_hessian;
   unsigned int seed;
-  int fused;                              // partition + histogram in one kernel (k_bt_expand): the built child is chosen from the estimates
   int reduce_in_select;                   // few features: the replay kernel reduces the per-feature results of a child (no last-arriver
                                           // reduction at the end of the split search)
   const unsigned char* feature_mask;      // [F] 1 = this tree may split on the feature (feature_fraction < 1), nullptr = all
@@ -113,6 +112,7 @@ class Booster {
   std::string SaveModelToString(int start_iteration, int num_iteration) const;
   std::string DumpModel(int start_iteration, int num_iteration, int importance_type) const;      // JSON (LGBM_BoosterDumpModel)
   int NumTrees() const { return static_cast<int>(models_.size()); }
+  int NumClasses() const { return K_; }
   int CurrentIteration() const { return iter_ + num_init_iteration_; }
   // LGBM_BoosterMerge (upstream GBDT::MergeFrom): the other booster's trees go in front of this one's; scores are not touched
   void MergeFrom(const Booster& other);
@@ -167,8 +167,12 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie } obj_ = kL2;
-  bool PointRegression() const { return obj_ == kL2 || obj_ >= kHuber; }
+  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass } obj_ = kL2;
+  bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie); }
+  // multiclass: K_ trees per iteration, one per class; scores / gradients are class-major [K_][n_]; cls_ = the class whose tree is being trained
+  int K_ = 1, cls_ = 0;
+  std::vector<double> class_init_probs_;
+  std::vector<char> class_need_train_;
   bool LogLink() const { return obj_ == kPoisson || obj_ == kGamma || obj_ == kTweedie; }      // predictions are exp(raw score)
   // kCustom: gradients come from the caller (objective=custom); kHuber.. : upstream regression_objective.hpp
   bool need_train_ = true, has_weights_ = false;
@@ -269,7 +273,7 @@ class Booster {
   int part_blocks_ = 888;                   // 6 x 148 SMs (k_bt_partition is built for 6 CTAs per SM)
   int idx_es_ = 2;                  // ints per index entry (2: quantized, 4: float mode)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_events_;
-  size_t hist_events_used_ = 0;
+  size_t hist_events_total_ = 0;      // events used by the running iteration (all of its trees)
   cudaEvent_t timer_ev_[2] = {nullptr, nullptr};
   // per-kernel-type timing with CUDA events (LGB_B200_PROFILE=1): development aid, breaks launch overlap
   bool prof_ = false;
@@ -289,9 +293,6 @@ class Booster {
   void PrepareGradients(bool absmax_ready);           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
-  void LaunchExpand();
-  bool fused_ = true;
-  size_t expand_smem_ = 0;
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
   void LaunchSelect(bool after_root);

@@ -18,7 +18,7 @@ namespace lgb {
 namespace {
 constexpr int kNumSms = 148;
 enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
-       kEvTweedie = 10 };   // (Booster has its own kL2: distinct names)
+       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -38,7 +38,8 @@ void Booster::InitMetrics() {
     }
   }
   if (names.empty() && obj_ != kCustom)      // the objective's default; a custom objective has none
-    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : cfg_.objective);
+    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : obj_ == kMulticlass ? "multi_logloss"
+                    : cfg_.objective);
   for (const std::string& m : names) {
     if (m == "None" || m == "none" || m == "null" || m == "na" || m == "custom") continue;
     if (m == "binary_logloss" || m == "binary") metrics_.push_back({kEvLogloss, "binary_logloss"});
@@ -51,6 +52,8 @@ void Booster::InitMetrics() {
     else if (m == "poisson") metrics_.push_back({kEvPoisson, "poisson"});
     else if (m == "gamma") metrics_.push_back({kEvGamma, "gamma"});
     else if (m == "tweedie") metrics_.push_back({kEvTweedie, "tweedie"});
+    else if (m == "multi_logloss" || m == "multiclass" || m == "softmax") metrics_.push_back({kEvMultiLogloss, "multi_logloss"});
+    else if (m == "multi_error") metrics_.push_back({kEvMultiError, "multi_error"});
     else if (m == "ndcg" || m == "lambdarank" || m == "rank_xendcg" || m == "xendcg") {
       std::vector<int> at = cfg_.eval_at;
       if (at.empty()) at = {1, 2, 3, 4, 5};
@@ -83,9 +86,9 @@ void Booster::AddValidData(Dataset* valid) {
   valids_.emplace_back();
   ValidSet& v = valids_.back();
   v.ds = valid;
-  v.score.AllocZero(std::max<int64_t>(valid->num_data, 1));
+  v.score.AllocZero(std::max<int64_t>(valid->num_data, 1) * K_);      // class-major [K][n]
   if (valid->has_init_score)
-    LGB_CUDA(cudaMemcpy(v.score.p, valid->d_init_score.p, sizeof(double) * valid->num_data, cudaMemcpyDeviceToDevice));
+    LGB_CUDA(cudaMemcpy(v.score.p, valid->d_init_score.p, sizeof(double) * valid->num_data * K_, cudaMemcpyDeviceToDevice));
 }
 
 // max DCG per query and position, and query weights (mean row weight), from the host copies of labels / weights
@@ -159,6 +162,16 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
   double h[kMaxEvalAt + 2];
   bool ndcg_done = false;
   for (const MetricSpec& m : metrics_) {
+    if (m.kind == kEvMultiLogloss || m.kind == kEvMultiError) {
+      LGB_CHECK(obj_ == kMulticlass, "metric=%s needs objective=multiclass", m.name.c_str());
+      k_metric_multi<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, K_, m.kind == kEvMultiLogloss ? 0 : 1, d_mpart_.p);
+      k_metric_final<<<1, kMetricThreads, 0, stream_>>>(d_mpart_.p, kMetricBlocks, d_mout_.p);
+      LGB_CUDA(cudaMemcpyAsync(h, d_mout_.p, sizeof(double) * 2, cudaMemcpyDeviceToHost, stream_));
+      LGB_CUDA(cudaStreamSynchronize(stream_));
+      out->push_back(h[0] / h[1]);
+      continue;
+    }
+    LGB_CHECK(obj_ != kMulticlass, "metric=%s is not defined for objective=multiclass (multi_logloss, multi_error)", m.name.c_str());
     if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || m.kind >= kEvHuber) {
       const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError
                        : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;

@@ -226,7 +226,9 @@ int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const voi
     ds->weight.assign(static_cast<const float*>(field_data), static_cast<const float*>(field_data) + num_element);
     ds->has_weight = true;
   } else if (name == "init_score") {
-    LGB_CHECK(type == C_API_DTYPE_FLOAT64 && num_element == ds->num_data, "init_score must be float64[num_data] (single class)");
+    LGB_CHECK(type == C_API_DTYPE_FLOAT64 && num_element >= ds->num_data && num_element % ds->num_data == 0,
+              "init_score must be float64[num_data * num_class], class-major");
+    ds->num_init_score_classes = static_cast<int>(num_element / ds->num_data);
     ds->init_score.assign(static_cast<const double*>(field_data), static_cast<const double*>(field_data) + num_element);
     ds->has_init_score = true;
   } else if (name == "group" || name == "query") {
@@ -322,9 +324,9 @@ int LGBM_BoosterDumpModel(BoosterHandle handle, int start_iteration, int num_ite
   API_END();
 }
 
-int LGBM_BoosterGetNumClasses(BoosterHandle, int* out_len) { API_BEGIN(); *out_len = 1; API_END(); }
+int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->NumClasses(); API_END(); }
 int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) { API_BEGIN(); *out_len = static_cast<Booster*>(handle)->NumTotalFeatures(); API_END(); }
-int LGBM_BoosterNumModelPerIteration(BoosterHandle, int* out) { API_BEGIN(); *out = 1; API_END(); }
+int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->NumClasses(); API_END(); }
 int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->NumTrees(); API_END(); }
 int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out) { API_BEGIN(); *out = static_cast<Booster*>(handle)->CurrentIteration(); API_END(); }
 
@@ -333,7 +335,7 @@ int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len,
   LGB_CHECK(data_idx == 0, "LGBM_BoosterGetPredict: only the training data (data_idx 0) is available");
   auto b = static_cast<Booster*>(handle);
   LGB_CHECK(!b->predict_only(), "LGBM_BoosterGetPredict: a booster loaded from a model string has no training data");
-  *out_len = b->train()->num_data;
+  *out_len = b->train()->num_data * b->NumClasses();      // class-major [num_class][num_data], as upstream
   b->CopyScores(out_result);
   API_END();
 }

@@ -119,7 +119,7 @@ void Config::Set(const std::string& params) {
   GET_D(sigmoid); GET_B(is_unbalance); GET_D(scale_pos_weight); GET_B(use_missing); GET_B(zero_as_missing);
   GET_B(feature_pre_filter); GET_B(use_quantized_grad); GET_I(num_grad_quant_bins); GET_B(stochastic_rounding);
   GET_B(quant_train_renew_leaf); GET_I(seed); GET_I(num_machines); GET_I(num_threads); GET_I(verbosity);
-  GET_B(lambdarank_norm);
+  GET_B(lambdarank_norm); GET_I(num_class);
   if (has("seed")) {      // upstream Config::Set: one LCG stream seeded with `seed` hands out the specific seeds, in this order
     HostRandom r(seed);
     r.NextShort(0, 32767);                          // data_random_seed (the host-side sample has its own)
@@ -144,6 +144,7 @@ void Config::Set(const std::string& params) {
   static const char* const kL2[] = {"regression_l2", "l2", "mean_squared_error", "mse", "l2_root", "root_mean_squared_error", "rmse"};
   for (auto a : kL2)
     if (objective == a) objective = "regression";
+  if (objective == "softmax") objective = "multiclass";
 }
 
 }  // namespace lgb

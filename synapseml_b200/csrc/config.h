@@ -43,6 +43,7 @@ struct Config {
   bool use_missing = true, zero_as_missing = false, feature_pre_filter = true;
   bool use_quantized_grad = false;
   int num_grad_quant_bins = 4;
+  int num_class = 1;
   bool stochastic_rounding = true;
   bool quant_train_renew_leaf = false;
   int seed = 0;

@@ -843,10 +843,11 @@ void Dataset::FreeSlots() {
 }
 
 void Dataset::InitStreaming(bool has_w, bool has_init, bool has_q, int nclasses, int nthreads) {
-  LGB_CHECK(nclasses <= 1, "Multiclass init scores (nclasses=%d) are not supported by this library yet", nclasses);
+  LGB_CHECK(nclasses >= 1, "InitStreaming: nclasses must be positive");
+  num_init_score_classes = nclasses;
   has_weight = has_w; has_init_score = has_init; has_query = has_q;
   if (has_w) weight.assign(num_data, 0.0f);
-  if (has_init) init_score.assign(num_data, 0.0);
+  if (has_init) init_score.assign(num_data * nclasses, 0.0);      // class-major [nclasses][num_data], upstream Metadata's layout
   if (has_q) query_id.assign(num_data, 0);
   EnsureSlots(std::max(nthreads, 1));
   streaming_inited = true;
@@ -983,7 +984,11 @@ void Dataset::PushRowsByCSR(const void* indptr, int indptr_type, const int32_t* 
 void Dataset::PushMetadata(int32_t nrow, int64_t start_row, const float* lab, const float* w, const double* init, const int32_t* q) {
   if (lab) std::copy(lab, lab + nrow, label.begin() + start_row);
   if (w && has_weight) std::copy(w, w + nrow, weight.begin() + start_row);
-  if (init && has_init_score) std::copy(init, init + nrow, init_score.begin() + start_row);
+  if (init && has_init_score) {
+    // a micro-batch carries its init scores class-major, [nclasses][nrow] (StreamingPartitionTask.scala:213-219)
+    for (int k = 0; k < num_init_score_classes; ++k)
+      std::copy(init + static_cast<size_t>(k) * nrow, init + static_cast<size_t>(k + 1) * nrow, init_score.begin() + static_cast<size_t>(k) * num_data + start_row);
+  }
   if (q && has_query) std::copy(q, q + nrow, query_id.begin() + start_row);
   bool all_in = false;
   {
@@ -1007,8 +1012,8 @@ void Dataset::MarkFinished() {
     LGB_CUDA(cudaMemcpy(d_weight.p, weight.data(), sizeof(float) * num_data, cudaMemcpyHostToDevice));
   }
   if (has_init_score) {
-    d_init_score.Alloc(std::max<int64_t>(num_data, 1));
-    LGB_CUDA(cudaMemcpy(d_init_score.p, init_score.data(), sizeof(double) * num_data, cudaMemcpyHostToDevice));
+    d_init_score.Alloc(std::max<size_t>(init_score.size(), 1));
+    LGB_CUDA(cudaMemcpy(d_init_score.p, init_score.data(), sizeof(double) * init_score.size(), cudaMemcpyHostToDevice));
   }
   if (has_query && query_boundaries.empty()) {
     // runs of equal consecutive group ids are queries (the streaming path pushes one id per row)

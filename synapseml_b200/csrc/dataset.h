@@ -97,6 +97,7 @@ class Dataset {
   std::string SerializeReference() const;
 
   void InitStreaming(bool has_w, bool has_init, bool has_q, int nclasses, int nthreads);
+  int num_init_score_classes = 1;       // init scores per row (multiclass: class-major [nclasses][num_data])
   float TimeBinning(const double* rows, int nrow, int repeats);      // measurement hook: ms per pass of the K2 kernel over nrow resident rows
   void PushRows(const void* data, int data_type, int32_t nrow, int32_t ncol, int64_t start_row, const float* lab,
                 const float* w, const double* init, const int32_t* q, int tid);

@@ -104,6 +104,35 @@ __global__ void k_grad_point(int kind, const double* __restrict__ score, const f
   }
 }
 
+// Multiclass softmax (upstream multiclass_objective.hpp, MulticlassSoftmax::GetGradients).  score / grad / hess are class-major
+// [K][n].  Per row: Common::Softmax over its K scores (subtract the maximum, exp, divide by the sum; exp is the software
+// function the oracle shares), g_k = p_k - [label == k], h_k = K / (K - 1) * p_k * (1 - p_k), times the row weight.
+constexpr int kMaxClasses = 64;
+__global__ void k_grad_multiclass(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
+                                  float* __restrict__ grad, float* __restrict__ hess, int n, int K, double factor) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    double rec[kMaxClasses];
+    double wmax = score[i];
+    for (int k = 0; k < K; ++k) { rec[k] = score[static_cast<size_t>(k) * n + i]; wmax = fmax(rec[k], wmax); }
+    double wsum = 0.0;
+    for (int k = 0; k < K; ++k) { rec[k] = SoftExp(rec[k] - wmax); wsum += rec[k]; }
+    const int lab = static_cast<int>(label[i]);
+    const bool has_w = weight != nullptr;
+    const float w = has_w ? weight[i] : 0.0f;
+    for (int k = 0; k < K; ++k) {
+      const double p = rec[k] / wsum;
+      const size_t idx = static_cast<size_t>(k) * n + i;
+      if (!has_w) {
+        grad[idx] = lab == k ? static_cast<float>(p - 1.0f) : static_cast<float>(p);
+        hess[idx] = static_cast<float>(factor * p * (1.0f - p));
+      } else {
+        grad[idx] = lab == k ? static_cast<float>((p - 1.0f) * w) : static_cast<float>(p * w);
+        hess[idx] = static_cast<float>(factor * p * (1.0f - p) * w);
+      }
+    }
+  }
+}
+
 // LambdaRank-NDCG.  One CTA per query.  Step 1: stable rank of every document by score (descending) by counting, which
 // equals std::stable_sort's order.  Step 2 (k_grad_lambdarank): the pair loop, with every floating-point sum taken in the
 // sequential loop's order so float32 lambdas / hessians and the double sum behind the log2 normalisation are bit-identical.

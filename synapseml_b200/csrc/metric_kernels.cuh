@@ -84,6 +84,40 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
   if (threadIdx.x == 0) partial[blockIdx.x] = make_double2(tl, tw);
 }
 
+// multi_logloss (kind 0) / multi_error (kind 1) on class-major scores [K][n] (upstream multiclass_metric.hpp): the loss sees the
+// softmax probabilities; multi_error counts a row as wrong when another class scores at least as high as its label's
+// (multi_error_top_k = 1).
+__global__ void __launch_bounds__(kMetricThreads) k_metric_multi(const double* __restrict__ score, const float* __restrict__ label,
+                                                                  const float* __restrict__ weight, long long n, int K, int kind,
+                                                                  double2* __restrict__ partial) {
+  __shared__ double s_w[8];
+  const double kEps = (double)1e-15f;
+  double sl = 0.0, sw = 0.0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int lab = static_cast<int>(label[i]);
+    const double w = weight ? static_cast<double>(weight[i]) : 1.0;
+    double wmax = score[i];
+    for (int k = 1; k < K; ++k) wmax = fmax(wmax, score[static_cast<size_t>(k) * n + i]);
+    double wsum = 0.0, pl = 0.0;
+    int num_larger = 0;
+    const double ref = score[static_cast<size_t>(lab) * n + i];
+    for (int k = 0; k < K; ++k) {
+      const double sc = score[static_cast<size_t>(k) * n + i];
+      const double e = exp(sc - wmax);
+      wsum += e;
+      if (k == lab) pl = e;
+      num_larger += sc >= ref;
+    }
+    double loss;
+    if (kind == 0) { const double p = pl / wsum; loss = p > kEps ? -log(p) : -log(kEps); }
+    else loss = num_larger > 1 ? 1.0 : 0.0;
+    sl += loss * w; sw += w;
+  }
+  const double tl = BlockSumD(sl, s_w);
+  const double tw = BlockSumD(sw, s_w);
+  if (threadIdx.x == 0) partial[blockIdx.x] = make_double2(tl, tw);
+}
+
 // one CTA: out[0..1] = sums of the partials in index order
 __global__ void __launch_bounds__(kMetricThreads) k_metric_final(const double2* __restrict__ partial, int n, double* __restrict__ out) {
   __shared__ double s_w[8];

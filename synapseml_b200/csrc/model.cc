@@ -95,10 +95,11 @@ std::string HostTree::ToString() const {
 }
 
 std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration) {
-  int first = std::max(0, start_iteration);
+  const int tpi = std::max(1, h.num_tree_per_iteration);
+  int first = std::min(std::max(0, start_iteration) * tpi, static_cast<int>(trees.size()));
   int last = static_cast<int>(trees.size());
-  if (num_iteration > 0) last = std::min(last, first + num_iteration);
-  std::string s = "tree\nversion=v3\nnum_class=1\nnum_tree_per_iteration=1\nlabel_index=0\n";
+  if (num_iteration > 0) last = std::min(last, first + num_iteration * tpi);
+  std::string s = "tree\nversion=v3\nnum_class=" + std::to_string(h.num_class) + "\nnum_tree_per_iteration=" + std::to_string(tpi) + "\nlabel_index=0\n";
   s += "max_feature_idx=" + std::to_string(h.max_feature_idx) + "\n";
   if (!h.objective.empty()) s += "objective=" + h.objective + "\n";
   s += "feature_names=";
@@ -227,8 +228,8 @@ void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostT
     else if (k == "objective") h->objective = v;
     else if (k == "feature_names") h->feature_names = SplitWs(v);
     else if (k == "feature_infos") h->feature_infos = SplitWs(v);
-    else if (k == "num_class") { if (atoi(v.c_str()) != 1) throw std::runtime_error("Model string: num_class != 1 is not supported by this library"); }
-    else if (k == "num_tree_per_iteration") { if (atoi(v.c_str()) != 1) throw std::runtime_error("Model string: num_tree_per_iteration != 1 is not supported by this library"); }
+    else if (k == "num_class") { h->num_class = atoi(v.c_str()); if (h->num_class < 1) throw std::runtime_error("Model string: bad num_class"); }
+    else if (k == "num_tree_per_iteration") { h->num_tree_per_iteration = atoi(v.c_str()); if (h->num_tree_per_iteration < 1) throw std::runtime_error("Model string: bad num_tree_per_iteration"); }
   }
   finish_tree();
   if (!saw_tree_word) throw std::runtime_error("Model string does not start with 'tree'");
@@ -274,10 +275,12 @@ std::string JsonEscape(const std::string& v) {
 
 std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration,
                         const std::vector<double>& importance) {
-  int first = std::max(0, start_iteration);
+  const int tpi = std::max(1, h.num_tree_per_iteration);
+  int first = std::min(std::max(0, start_iteration) * tpi, static_cast<int>(trees.size()));
   int last = static_cast<int>(trees.size());
-  if (num_iteration > 0) last = std::min(last, first + num_iteration);
-  std::string s = "{\"name\":\"tree\",\n\"version\":\"v3\",\n\"num_class\":1,\n\"num_tree_per_iteration\":1,\n\"label_index\":0,\n";
+  if (num_iteration > 0) last = std::min(last, first + num_iteration * tpi);
+  std::string s = "{\"name\":\"tree\",\n\"version\":\"v3\",\n\"num_class\":" + std::to_string(h.num_class) + ",\n\"num_tree_per_iteration\":" +
+                  std::to_string(tpi) + ",\n\"label_index\":0,\n";
   s += "\"max_feature_idx\":" + std::to_string(h.max_feature_idx) + ",\n";
   if (!h.objective.empty()) s += "\"objective\":\"" + JsonEscape(h.objective) + "\",\n";
   s += "\"average_output\":false,\n\"feature_names\":[";

@@ -28,12 +28,14 @@ struct HostTree {
 
 struct ModelHeader {
   int max_feature_idx = 0;
+  int num_class = 1, num_tree_per_iteration = 1;      // multiclass: one tree per class and iteration, class k's trees are k, k + K, ...
   std::string objective;
   std::vector<std::string> feature_names;
   std::vector<std::string> feature_infos;
   std::vector<std::pair<std::string, std::string>> parameters;
 };
 
+// start_iteration / num_iteration count ITERATIONS (num_tree_per_iteration trees each)
 std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration);
 // JSON dump of the same model (upstream GBDT::DumpModel / Tree::ToJSON): what LGBM_BoosterDumpModel returns to
 // lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:480-499 (dumpModel).
@@ -41,7 +43,7 @@ std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& tre
 std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration,
                         const std::vector<double>& importance);
 
-// Inverse of ModelToString for the subset this library writes (num_class = 1, no categorical splits, no linear trees):
+// Inverse of ModelToString for the subset this library writes (no categorical splits, no linear trees):
 // what LGBM_BoosterLoadModelFromString reads when the Scala side rebuilds a booster from the model string on an executor
 // (lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:41-49).  Throws
 // std::runtime_error on malformed input.

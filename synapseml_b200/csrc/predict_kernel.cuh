@@ -27,40 +27,52 @@ struct PredModelDev {
 constexpr int kPredictRaw = 1, kPredictNormal = 0, kPredictLeaf = 2;
 
 // rows: element (r, c) at rows[r * row_stride + c * col_stride] (row- or column-major, float or double).
-// out: raw / normal: [nrow]; leaf index: [nrow][t1 - t0].
+// Trees [t0, t1) of a model with K trees per iteration (tree t belongs to class t % K; t0 and t1 are multiples of K).
+// out: raw / normal: [nrow][K]; leaf index: [nrow][t1 - t0].  Normal output: sigmoid_on 1 = sigmoid, 2 = exp (log-link regression),
+// 3 = softmax over the row's K raw scores (Common::Softmax: subtract the maximum, exp, divide by the sum).
 template <typename T>
 __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long row_stride, long long col_stride, PredModelDev m, int t0,
-                          int t1, int mode, int sigmoid_on, double sigmoid, double* __restrict__ out) {
+                          int t1, int K, int mode, int sigmoid_on, double sigmoid, double* __restrict__ out) {
   const double kZero = (double)1e-35f;
   for (long long r = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; r < nrow; r += static_cast<long long>(gridDim.x) * blockDim.x) {
     const T* row = rows + r * row_stride;
-    double acc = 0.0;
-    for (int t = t0; t < t1; ++t) {
-      const int no = m.node_off[t], lo = m.leaf_off[t];
-      int leaf = 0;
-      if (m.node_off[t + 1] > no) {
-        int node = 0;
-        do {
-          const int g = no + node;
-          double fval = static_cast<double>(row[static_cast<long long>(m.split_feature[g]) * col_stride]);
-          const int dt = m.decision_type[g];
-          const int mt = (dt >> 2) & 3;
-          const bool is_nan = fval != fval;
-          if (is_nan && mt != 2) fval = 0.0;
-          bool left;
-          if ((mt == 1 && fval >= -kZero && fval <= kZero) || (mt == 2 && is_nan)) left = (dt & 2) != 0;
-          else left = fval <= m.threshold[g];
-          node = left ? m.left[g] : m.right[g];
-        } while (node >= 0);
-        leaf = ~node;
+    for (int cls = 0; cls < K; ++cls) {
+      double acc = 0.0;
+      for (int t = t0 + cls; t < t1; t += K) {
+        const int no = m.node_off[t], lo = m.leaf_off[t];
+        int leaf = 0;
+        if (m.node_off[t + 1] > no) {
+          int node = 0;
+          do {
+            const int g = no + node;
+            double fval = static_cast<double>(row[static_cast<long long>(m.split_feature[g]) * col_stride]);
+            const int dt = m.decision_type[g];
+            const int mt = (dt >> 2) & 3;
+            const bool is_nan = fval != fval;
+            if (is_nan && mt != 2) fval = 0.0;
+            bool left;
+            if ((mt == 1 && fval >= -kZero && fval <= kZero) || (mt == 2 && is_nan)) left = (dt & 2) != 0;
+            else left = fval <= m.threshold[g];
+            node = left ? m.left[g] : m.right[g];
+          } while (node >= 0);
+          leaf = ~node;
+        }
+        if (mode == kPredictLeaf) out[r * (t1 - t0) + (t - t0)] = static_cast<double>(leaf);
+        else acc += m.leaf_value[lo + leaf];
       }
-      if (mode == kPredictLeaf) out[r * (t1 - t0) + (t - t0)] = static_cast<double>(leaf);
-      else acc += m.leaf_value[lo + leaf];
+      if (mode != kPredictLeaf) {
+        if (mode == kPredictNormal && sigmoid_on == 1) acc = 1.0 / (1.0 + SoftExp(-sigmoid * acc));
+        else if (mode == kPredictNormal && sigmoid_on == 2) acc = SoftExp(acc);      // log-link regression objectives
+        out[r * K + cls] = acc;
+      }
     }
-    if (mode != kPredictLeaf) {
-      if (mode == kPredictNormal && sigmoid_on == 1) acc = 1.0 / (1.0 + SoftExp(-sigmoid * acc));
-      else if (mode == kPredictNormal && sigmoid_on == 2) acc = SoftExp(acc);      // log-link regression objectives
-      out[r] = acc;
+    if (mode == kPredictNormal && sigmoid_on == 3) {
+      double* o = out + r * K;
+      double wmax = o[0];
+      for (int k = 1; k < K; ++k) wmax = fmax(wmax, o[k]);
+      double wsum = 0.0;
+      for (int k = 0; k < K; ++k) { o[k] = SoftExp(o[k] - wmax); wsum += o[k]; }
+      for (int k = 0; k < K; ++k) o[k] /= wsum;
     }
   }
 }

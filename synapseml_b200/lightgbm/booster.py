@@ -140,10 +140,17 @@ class LightGBMBooster:
                  "Booster Get Eval Results for data index: %d" % data_index)
         return list(zip(eval_names, out[:len(eval_names)].tolist()))
 
+    def num_classes(self):
+        """getNumClasses (LightGBMBooster.scala:160-168): 1 unless the objective is multiclass."""
+        k = C.c_int()
+        validate(lightgbmlib().LGBM_BoosterGetNumClasses(self.booster_handle, C.byref(k)), "Booster NumClasses")
+        return k.value
+
     def inner_predict(self, data_index=0):
+        """Training scores; multiclass: class-major [num_class * num_data]."""
         lib = lightgbmlib()
         out_len = C.c_int64()
-        out = np.zeros(self._train_rows, dtype=np.float64)
+        out = np.zeros(self._train_rows * self.num_classes(), dtype=np.float64)
         validate(lib.LGBM_BoosterGetPredict(self.booster_handle, C.c_int(data_index), C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))),
                  "Booster get predict")
         return out[:out_len.value]

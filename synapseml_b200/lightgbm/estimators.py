@@ -207,7 +207,7 @@ class LightGBMBase:
             counts = [None] * world
             dist.all_gather_object(counts, local_rows)
             total_rows = int(sum(counts))
-        train_params = self.get_train_params(world, num_tasks_per_exec)
+        train_params = self.add_custom_train_params(self.get_train_params(world, num_tasks_per_exec), df, dist if dist_on else None)
         ds_params = dataset_creation_params(self.getMaxBin(), self.getBinSampleCount(), self.getMinDataInLeaf(),
                                             train_params.executionParams.numThreads,
                                             data_random_seed=g["dataRandomSeed"] if g["dataRandomSeed"] is not None else g["seed"])
@@ -250,6 +250,10 @@ class LightGBMBase:
             model_str = payload[0]
         return self._make_model(model_str)
 
+    def add_custom_train_params(self, train_params, df, dist):
+        """LightGBMBase.addCustomTrainParams: estimator-specific additions that need the data (the classifier's numClass)."""
+        return train_params
+
     def getPerformanceMeasures(self):
         return self.performance_measures
 
@@ -286,7 +290,10 @@ class LightGBMModelBase:
             f.write(self.model_str)
 
     def predict_raw(self, features):
-        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_RAW)
+        """Raw scores: [n], or [n, num_class] for a multiclass model."""
+        raw = self._native().predict_for_mat(features, LightGBMBooster.PREDICT_RAW)
+        K = self._model.num_tree_per_iteration
+        return raw if K == 1 else raw.reshape(-1, K)
 
     def predict_leaf(self, features):
         return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
@@ -299,6 +306,9 @@ class LightGBMClassificationModel(LightGBMModelBase):
     def transform(self, features):
         raw = self.predict_raw(features)
         p = self._native().predict_for_mat(features, LightGBMBooster.PREDICT_NORMAL)
+        K = self._model.num_tree_per_iteration
+        if K > 1:      # multiclass: one raw score / probability per class (LightGBMBooster.scala:559-575), prediction = arg max
+            return dict(rawPrediction=raw, probability=p.reshape(-1, K), prediction=np.argmax(raw, axis=1).astype(np.float64))
         # binary: the native value is the positive-class score; expanded as the reference does (LightGBMBooster.scala:559-575)
         return dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1), prediction=(p > 0.5).astype(np.float64))
 
@@ -322,10 +332,22 @@ class LightGBMClassifier(LightGBMBase):
         return dict(isUnbalance=False, boostFromAverage=True)
 
     def get_train_params(self, num_tasks, num_tasks_per_exec):
-        if self._p["objective"] != "binary":
-            raise NotImplementedError("only objective=binary is built for the classifier (multiclass: later row)")
         return ClassifierTrainParams(isUnbalance=self._p["isUnbalance"], boostFromAverage=self._p["boostFromAverage"],
-                                     **self._common_groups(num_tasks, num_tasks_per_exec))
+                                     numClass=getattr(self, "_num_class", 1), **self._common_groups(num_tasks, num_tasks_per_exec))
+
+    def add_custom_train_params(self, train_params, df, dist):
+        """LightGBMClassifier.addCustomTrainParams (LightGBMClassifier.scala:59-67): for anything but the binary objective the number
+        of classes is inferred from the data — Spark's getNumClasses without label metadata: the largest label + 1."""
+        if self._p["objective"] == "binary":
+            return train_params
+        local = max((int(np.max(p["label"])) for p in df.partitions if len(p["label"])), default=0)
+        if dist is not None:
+            allmax = [None] * dist.get_world_size()
+            dist.all_gather_object(allmax, local)
+            local = max(allmax)
+        self._num_class = local + 1
+        train_params.numClass = self._num_class
+        return train_params
 
     def _make_model(self, model_str):
         return LightGBMClassificationModel(model_str)

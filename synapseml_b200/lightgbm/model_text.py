@@ -73,19 +73,26 @@ class TextModel:
                         k, v = l[1:-1].split(": ", 1)
                         self.parameters[k] = v
         self.objective = self.header.get("objective", "")
+        self.num_class = int(self.header.get("num_class", 1))
+        self.num_tree_per_iteration = int(self.header.get("num_tree_per_iteration", 1))      # tree t belongs to class t % K
         self.max_feature_idx = int(self.header.get("max_feature_idx", -1))
         self.feature_names = self.header.get("feature_names", "").split()
 
     def predict_raw(self, X, num_iteration=None):
+        """Raw scores: [n] for one tree per iteration, [n, K] for K (multiclass)."""
         X = np.asarray(X, dtype=np.float64)
-        out = np.zeros(X.shape[0], dtype=np.float64)
-        trees = self.trees if num_iteration is None else self.trees[:num_iteration]
-        for t in trees:
-            out += t.predict(X)
-        return out
+        K = self.num_tree_per_iteration
+        out = np.zeros((X.shape[0], K), dtype=np.float64)
+        trees = self.trees if num_iteration is None else self.trees[:num_iteration * K]
+        for i, t in enumerate(trees):
+            out[:, i % K] += t.predict(X)
+        return out[:, 0] if K == 1 else out
 
     def predict(self, X):
         raw = self.predict_raw(X)
+        if self.objective.startswith("multiclass"):
+            e = np.exp(raw - raw.max(axis=1, keepdims=True))
+            return e / e.sum(axis=1, keepdims=True)
         if self.objective.startswith("binary"):
             sig = 1.0
             for tok in self.objective.split():

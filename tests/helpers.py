@@ -125,14 +125,20 @@ class NativeBooster:
         assert n.value <= len(sb)
         return sb.value.decode()
 
+    def num_classes(self):
+        k = C.c_int()
+        validate(self.lib.LGBM_BoosterGetNumClasses(self.handle, C.byref(k)))
+        return k.value
+
     def scores(self):
-        sc = np.zeros(self.ds.n)
+        sc = np.zeros(self.ds.n * self.num_classes())      # multiclass: class-major
         n64 = C.c_int64()
         validate(self.lib.LGBM_BoosterGetPredict(self.handle, 0, C.byref(n64), sc.ctypes.data_as(C.POINTER(C.c_double))))
         return sc
 
     def gradients(self):
-        g, h = np.zeros(self.ds.n, dtype=np.float32), np.zeros(self.ds.n, dtype=np.float32)
+        n = self.ds.n * self.num_classes()
+        g, h = np.zeros(n, dtype=np.float32), np.zeros(n, dtype=np.float32)
         validate(self.lib.LGBM_B200_BoosterGetGradients(self.handle, g.ctypes.data_as(C.POINTER(C.c_float)), h.ctypes.data_as(C.POINTER(C.c_float))))
         return g, h
 
