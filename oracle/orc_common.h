@@ -184,6 +184,10 @@ struct Config {
   int feature_fraction_seed = 2;
   double bagging_fraction = 1.0;
   int bagging_freq = 0, bagging_seed = 3;
+  // boosting = dart / goss (upstream config.h defaults)
+  double drop_rate = 0.1, skip_drop = 0.5, top_rate = 0.2, other_rate = 0.1;
+  int max_drop = 50, drop_seed = 4;
+  bool uniform_drop = false, xgboost_dart_mode = false;
   int num_machines = 1;
   int num_threads = 0;
   int verbosity = 1;
@@ -297,7 +301,7 @@ struct Config {
       const int int_max = 32767;
       r.NextShort(0, int_max);                       // data_random_seed
       bagging_seed = r.NextShort(0, int_max);
-      r.NextShort(0, int_max);                       // drop_seed
+      drop_seed = r.NextShort(0, int_max);
       feature_fraction_seed = r.NextShort(0, int_max);
     }
     getd("alpha", &alpha);
@@ -309,6 +313,10 @@ struct Config {
     getd("bagging_fraction", &bagging_fraction);
     geti("bagging_freq", &bagging_freq);
     geti("bagging_seed", &bagging_seed);
+    getd("drop_rate", &drop_rate); getd("skip_drop", &skip_drop); getd("top_rate", &top_rate); getd("other_rate", &other_rate);
+    geti("max_drop", &max_drop); geti("drop_seed", &drop_seed); getb("uniform_drop", &uniform_drop); getb("xgboost_dart_mode", &xgboost_dart_mode);
+    if (boosting == "random_forest") boosting = "rf";
+    if (boosting == "gbrt") boosting = "gbdt";
     geti("num_machines", &num_machines);
     geti("num_threads", &num_threads);
     geti("verbosity", &verbosity);

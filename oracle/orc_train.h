@@ -263,6 +263,13 @@ class Booster {
   int iter = 0;
   // objective state
   enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS } obj = OBJ_L2;
+  enum Boost { BOOST_GBDT, BOOST_RF, BOOST_DART, BOOST_GOSS } boost = BOOST_GBDT;
+  double shrinkage_rate = 0.1;             // learning_rate, except under DART, which rescales it by the number of dropped trees
+  std::vector<double> rf_init_scores;      // RF: the automatic initial scores (never added to the scores; every tree carries them)
+  Random drop_rand;                        // DART: random_for_drop_
+  std::vector<double> tree_weight;         // DART: one weight per iteration
+  double sum_weight = 0.0;
+  std::vector<int> drop_index;
   int K = 1;                               // trees per iteration (num_class for multiclass)
   int cur_class = 0;
   std::vector<double> class_init_probs;    // multiclass: (weighted) share of every label over all machines
@@ -318,11 +325,19 @@ class Booster {
     total_rows = off;
     has_weights = ds[0]->has_weight;
     sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf};
-    if (cfg.boosting != "gbdt") throw std::runtime_error("oracle: only boosting=gbdt is restated");
+    if (cfg.boosting == "gbdt") boost = BOOST_GBDT;
+    else if (cfg.boosting == "rf") boost = BOOST_RF;
+    else if (cfg.boosting == "dart") boost = BOOST_DART;
+    else if (cfg.boosting == "goss") boost = BOOST_GOSS;
+    else throw std::runtime_error("oracle: boosting=" + cfg.boosting + " is not restated");
+    shrinkage_rate = boost == BOOST_RF ? 1.0 : cfg.learning_rate;
+    drop_rand = Random(cfg.drop_seed);
     if (cfg.zero_as_missing) throw std::runtime_error("oracle: zero_as_missing is not restated");
     feature_rand = Random(cfg.feature_fraction_seed);
     tree_mask.assign(F, 1);
-    bagging = cfg.bagging_freq > 0 && cfg.bagging_fraction < 1.0;
+    bagging = (cfg.bagging_freq > 0 && cfg.bagging_fraction < 1.0) || boost == BOOST_GOSS;
+    if (boost == BOOST_RF && !(bagging || cfg.feature_fraction < 1.0))
+      throw std::runtime_error("oracle: boosting=rf needs bagging (bagging_freq > 0, bagging_fraction < 1) or feature_fraction < 1");
     for (auto& sh : shards) {
       const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
       sh.bag_cnt = n;
@@ -338,6 +353,7 @@ class Booster {
   // the stream of its 1024-row block and is in the bag when the draw is below bagging_fraction.  (The subset copy upstream makes
   // for small bags changes no tree; the discretizer then sees the bag only — this restatement always uses all rows for the scales.)
   void Bagging() {
+    if (boost == BOOST_GOSS) { GossSample(); return; }
     if (!bagging || iter % cfg.bagging_freq != 0) return;
     for (auto& sh : shards) {
       const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
@@ -347,6 +363,138 @@ class Booster {
         else sh.bag_indices[--right] = i;
       }
       sh.bag_cnt = left;
+    }
+  }
+
+  // GOSS (upstream src/boosting/goss.hpp, BaggingHelper): no sampling during the first 1 / learning_rate iterations; afterwards, per
+  // block of rows, the top_rate share with the largest sum over classes of |g * h| is kept and other_rate of the rest is drawn
+  // sequentially from the block's LCG stream, its gradients scaled by (cnt - top_k) / other_k.  Upstream cuts the rows into blocks
+  // by its OpenMP thread count (at least 1024 rows each); this restatement uses one block per 1024 rows.
+  void GossSample() {
+    for (auto& sh : shards) {
+      const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
+      if (iter < static_cast<int>(1.0f / cfg.learning_rate)) {
+        for (data_size_t i = 0; i < n; ++i) sh.bag_indices[i] = i;
+        sh.bag_cnt = n;
+        continue;
+      }
+      std::vector<std::pair<std::vector<data_size_t>, std::vector<data_size_t>>> parts((n + 1023) / 1024);
+#pragma omp parallel for schedule(dynamic)
+      for (data_size_t b = 0; b < (n + 1023) / 1024; ++b) {
+        const data_size_t start = b * 1024, cnt = std::min<data_size_t>(1024, n - start);
+        std::vector<score_t> tmp(cnt, 0.0f);
+        auto mag = [&](data_size_t i) {
+          score_t a = 0.0f;
+          if (K == 1) a += std::fabs(sh.grad[start + i] * sh.hess[start + i]);
+          else for (int k = 0; k < K; ++k) a += std::fabs(sh.grad_k[k][start + i] * sh.hess_k[k][start + i]);
+          return a;
+        };
+        for (data_size_t i = 0; i < cnt; ++i) tmp[i] = mag(i);
+        data_size_t top_k = static_cast<data_size_t>(cnt * cfg.top_rate);
+        const data_size_t other_k = static_cast<data_size_t>(cnt * cfg.other_rate);
+        top_k = std::max<data_size_t>(1, top_k);
+        std::vector<score_t> sorted(tmp);
+        std::nth_element(sorted.begin(), sorted.begin() + (top_k - 1), sorted.end(), std::greater<score_t>());      // ArgMaxAtK
+        const score_t threshold = sorted[top_k - 1];
+        const score_t multiply = static_cast<score_t>(cnt - top_k) / other_k;
+        data_size_t big = 0;
+        auto& left = parts[b].first; auto& right = parts[b].second;
+        for (data_size_t i = 0; i < cnt; ++i) {
+          if (tmp[i] >= threshold) { left.push_back(start + i); ++big; continue; }
+          const data_size_t sampled = static_cast<data_size_t>(left.size()) - big;
+          const data_size_t rest_need = other_k - sampled;
+          const data_size_t rest_all = (cnt - i) - (top_k - big);
+          const double prob = rest_need / static_cast<double>(rest_all);
+          if (sh.bag_rands[b].NextFloat() < prob) {
+            left.push_back(start + i);
+            if (K == 1) { sh.grad[start + i] *= multiply; sh.hess[start + i] *= multiply; }
+            else for (int k = 0; k < K; ++k) { sh.grad_k[k][start + i] *= multiply; sh.hess_k[k][start + i] *= multiply; }
+          } else {
+            right.push_back(start + i);
+          }
+        }
+      }
+      data_size_t l = 0, r = n;
+      for (auto& p : parts) {      // in-bag rows ascending in front, the others behind them
+        for (data_size_t v : p.first) sh.bag_indices[l++] = v;
+        for (data_size_t v : p.second) sh.bag_indices[--r] = v;
+      }
+      sh.bag_cnt = l;
+    }
+  }
+
+  // ScoreUpdater::AddScore(tree, class): every row walks the tree over its bins
+  void AddTreeToScores(const Tree& t, int k) {
+    for (auto& sh : shards) {
+      std::vector<double>& sc = (obj == OBJ_MULTICLASS) ? sh.score_k[k] : sh.score;
+      const int64_t n = sh.ds->num_data;
+#pragma omp parallel for schedule(static)
+      for (int64_t i = 0; i < n; ++i) sc[i] += t.leaf_value[LeafByBins(t, sh.ds, static_cast<data_size_t>(i))];
+    }
+  }
+
+  // DART::DroppingTrees (upstream src/boosting/dart.hpp): picks the iterations to drop, takes their trees out of the training
+  // scores and sets this iteration's shrinkage
+  void DroppingTrees() {
+    drop_index.clear();
+    const bool is_skip = drop_rand.NextFloat() < cfg.skip_drop;
+    if (!is_skip) {
+      double drop_rate = cfg.drop_rate;
+      if (!cfg.uniform_drop) {
+        const double inv_average_weight = static_cast<double>(tree_weight.size()) / sum_weight;
+        if (cfg.max_drop > 0) drop_rate = std::min(drop_rate, cfg.max_drop * inv_average_weight / sum_weight);
+        for (int i = 0; i < iter; ++i) {
+          if (drop_rand.NextFloat() < drop_rate * tree_weight[i] * inv_average_weight) {
+            drop_index.push_back(i);
+            if (drop_index.size() >= static_cast<size_t>(cfg.max_drop)) break;
+          }
+        }
+      } else {
+        if (cfg.max_drop > 0) drop_rate = std::min(drop_rate, cfg.max_drop / static_cast<double>(iter));
+        for (int i = 0; i < iter; ++i) {
+          if (drop_rand.NextFloat() < drop_rate) {
+            drop_index.push_back(i);
+            if (drop_index.size() >= static_cast<size_t>(cfg.max_drop)) break;
+          }
+        }
+      }
+    }
+    for (int i : drop_index) {
+      for (int k = 0; k < K; ++k) {
+        Tree& t = *models[static_cast<size_t>(i) * K + k];
+        t.Shrinkage(-1.0);
+        AddTreeToScores(t, k);
+      }
+    }
+    if (!cfg.xgboost_dart_mode) shrinkage_rate = cfg.learning_rate / (1.0f + static_cast<double>(drop_index.size()));
+    else if (drop_index.empty()) shrinkage_rate = cfg.learning_rate;
+    else shrinkage_rate = cfg.learning_rate / (cfg.learning_rate + static_cast<double>(drop_index.size()));
+  }
+
+  // DART::Normalize: the dropped trees come back scaled by k / (k + 1) (xgboost mode: k / (k + learning_rate))
+  void Normalize() {
+    const double k = static_cast<double>(drop_index.size());
+    for (int i : drop_index) {
+      for (int c = 0; c < K; ++c) {
+        Tree& t = *models[static_cast<size_t>(i) * K + c];
+        if (!cfg.xgboost_dart_mode) {
+          t.Shrinkage(1.0f / (k + 1.0f));      // (validation scores would take the tree here)
+          t.Shrinkage(-k);
+        } else {
+          t.Shrinkage(shrinkage_rate);
+          t.Shrinkage(-k / cfg.learning_rate);
+        }
+        AddTreeToScores(t, c);
+      }
+      if (!cfg.uniform_drop) {
+        if (!cfg.xgboost_dart_mode) {
+          sum_weight -= tree_weight[i] * (1.0f / (k + 1.0f));
+          tree_weight[i] *= (k / (k + 1.0f));
+        } else {
+          sum_weight -= tree_weight[i] * (1.0f / (k + cfg.learning_rate));
+          tree_weight[i] *= (k / (k + cfg.learning_rate));
+        }
+      }
     }
   }
 
@@ -913,6 +1061,7 @@ class Booster {
       if (S > 1) { double acc = 0.0; for (int s = 0; s < S; ++s) acc += v; v = acc / S; }
       return v;
     };
+    if (boost == BOOST_RF) return TrainOneIterRF(enter_class, leave_class, automatic_init_score);
     // GBDT::BoostFromAverage (upstream src/boosting/gbdt.cpp), once per class
     std::vector<double> init_scores(K, 0.0);
     if (!custom) {
@@ -928,6 +1077,7 @@ class Booster {
         leave_class(k, false);
       }
     }
+    if (boost == BOOST_DART) DroppingTrees();      // DART::GetTrainingScore: before the gradients are taken
     if (custom) {
       size_t off = 0;
       for (auto& sh : shards) {
@@ -946,7 +1096,7 @@ class Booster {
       if (train_this && F > 0) tree = TrainTree();
       if (tree->num_leaves > 1) {
         should_continue = true;
-        tree->Shrinkage(cfg.learning_rate);
+        tree->Shrinkage(shrinkage_rate);
         for (auto& sh : shards) {
           for (int l = 0; l < tree->num_leaves; ++l) {
             const double out = tree->leaf_value[l];
@@ -977,6 +1127,70 @@ class Booster {
       if (static_cast<int>(models.size()) > K) for (int k = 0; k < K; ++k) models.pop_back();
       return true;
     }
+    ++iter;
+    if (boost == BOOST_DART) {      // DART::TrainOneIter, after GBDT::TrainOneIter (which has advanced iter_)
+      Normalize();
+      if (!cfg.uniform_drop) { tree_weight.push_back(shrinkage_rate); sum_weight += shrinkage_rate; }
+    }
+    return false;
+  }
+
+  // RF::TrainOneIter (upstream src/boosting/rf.hpp): gradients are taken ONCE, at the automatic initial scores; every tree is fit to
+  // them on its own bag, carries the initial score as a bias, and the scores hold the running average of the trees.
+  template <typename EnterFn, typename LeaveFn, typename InitFn>
+  bool TrainOneIterRF(EnterFn enter_class, LeaveFn leave_class, InitFn automatic_init_score) {
+    const bool multi = obj == OBJ_MULTICLASS;
+    if (iter == 0 && rf_init_scores.empty()) {      // RF::Boosting
+      rf_init_scores.assign(K, 0.0);
+      for (int k = 0; k < K; ++k) {
+        cur_class = k;
+        if (!shards[0].ds->has_init_score && (cfg.boost_from_average || F == 0)) {
+          const double v = automatic_init_score();
+          if (std::fabs(v) > kEpsilon) rf_init_scores[k] = v;
+        }
+      }
+      // gradients at the constant scores: the score arrays are borrowed for the call
+      std::vector<std::vector<std::vector<double>>> saved_k;
+      std::vector<std::vector<double>> saved;
+      for (auto& sh : shards) {
+        if (multi) { saved_k.push_back(sh.score_k); for (int k = 0; k < K; ++k) std::fill(sh.score_k[k].begin(), sh.score_k[k].end(), rf_init_scores[k]); }
+        else { saved.push_back(sh.score); std::fill(sh.score.begin(), sh.score.end(), rf_init_scores[0]); }
+      }
+      GetGradients();
+      for (size_t s = 0; s < shards.size(); ++s) { if (multi) shards[s].score_k = saved_k[s]; else shards[s].score = saved[s]; }
+    }
+    Bagging();
+    for (int k = 0; k < K; ++k) {
+      enter_class(k, true);
+      const bool train_this = multi ? class_need_train[k] != 0 : need_train;
+      std::unique_ptr<Tree> tree(new Tree(2));
+      if (train_this && F > 0) tree = TrainTree();
+      bool add = false;
+      if (tree->num_leaves > 1) {
+        if (std::fabs(rf_init_scores[k]) > kEpsilon) tree->AddBias(rf_init_scores[k]);
+        add = true;
+      } else if (static_cast<int>(models.size()) < K) {
+        double output = 0.0;
+        if (!train_this) { if (obj != OBJ_CUSTOM) output = BoostFromScore(); } else output = rf_init_scores[k];
+        tree->AsConstantTree(output);
+        add = true;
+      }
+      if (add) {      // MultiplyScore(iter), UpdateScore(tree), MultiplyScore(1 / (iter + 1))
+        const double pre = static_cast<double>(iter), post = 1.0 / (iter + 1);
+        for (auto& sh : shards) {
+          const int64_t n = sh.ds->num_data;
+#pragma omp parallel for schedule(static)
+          for (int64_t i = 0; i < n; ++i) {
+            double v = sh.score[i] * pre;
+            v += tree->leaf_value[LeafByBins(*tree, sh.ds, static_cast<data_size_t>(i))];
+            sh.score[i] = v * post;
+          }
+        }
+      }
+      models.push_back(std::move(tree));
+      leave_class(k, true);
+    }
+    cur_class = 0;
     ++iter;
     return false;
   }
@@ -1018,6 +1232,7 @@ class Booster {
     s += "label_index=0\n";
     s += "max_feature_idx=" + std::to_string(d->num_total_features - 1) + "\n";
     if (!ObjectiveString().empty()) s += "objective=" + ObjectiveString() + "\n";      // none without an objective function
+    if (boost == BOOST_RF) s += "average_output\n";
     s += "feature_names=";
     for (int j = 0; j < d->num_total_features; ++j) { if (j) s += ' '; s += d->feature_names[j]; }
     s += "\nfeature_infos=";

@@ -1011,6 +1011,85 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
   LGB_TRACE(ctrl, 42);
 }
 
+// ------------------------------------------------------------------------------------------------ GOSS
+// Gradient-based one-side sampling (upstream src/boosting/goss.hpp, BaggingHelper), one CTA per block of 1024 rows: the top_rate
+// share of the block with the largest sum over classes of |g * h| is kept, other_rate of the rest is drawn sequentially from the
+// block's LCG stream (the chance of a row depends on how many were drawn before it) and has its gradients scaled by
+// (cnt - top_k) / other_k.  Writes the bag as a bit per row and adds the bag size to *count.
+__global__ void __launch_bounds__(256) k_goss_sample(float* __restrict__ grad, float* __restrict__ hess, int n, int K, double top_rate,
+                                                     double other_rate, unsigned int* __restrict__ rand_state, unsigned int* __restrict__ bits,
+                                                     int* __restrict__ count) {
+  __shared__ float s_mag[1024];
+  __shared__ unsigned int s_bag[32], s_mul[32];
+  __shared__ float s_threshold;
+  const int blk = blockIdx.x;
+  const int start = blk * 1024;
+  const int cnt = min(1024, n - start);
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+    float a = 0.0f;
+    if (i < cnt) for (int k = 0; k < K; ++k) a += fabsf(grad[static_cast<size_t>(k) * n + start + i] * hess[static_cast<size_t>(k) * n + start + i]);
+    s_mag[i] = a;
+  }
+  if (threadIdx.x < 32) { s_bag[threadIdx.x] = 0u; s_mul[threadIdx.x] = 0u; }
+  __syncthreads();
+  int top_k = static_cast<int>(cnt * top_rate);
+  const int other_k = static_cast<int>(cnt * other_rate);
+  top_k = max(1, top_k);
+  // the top_k-th largest magnitude (ArrayArgs::ArgMaxAtK): the value whose rank, ties broken by position, is top_k - 1
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const float v = s_mag[i];
+    int rank = 0;
+    for (int j = 0; j < cnt; ++j) { const float u = s_mag[j]; rank += (u > v) || (u == v && j < i); }
+    if (rank == top_k - 1) s_threshold = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float threshold = s_threshold;
+    unsigned int x = rand_state[blk];
+    int left = 0, big = 0;
+    for (int i = 0; i < cnt; ++i) {
+      if (s_mag[i] >= threshold) { s_bag[i >> 5] |= 1u << (i & 31); ++left; ++big; continue; }
+      const int sampled = left - big;
+      const int rest_need = other_k - sampled;
+      const int rest_all = (cnt - i) - (top_k - big);
+      const double prob = rest_need / static_cast<double>(rest_all);
+      x = 214013u * x + 2531011u;
+      const float u = static_cast<float>((x >> 16) & 0x7FFF) / 32768.0f;
+      if (static_cast<double>(u) < prob) { s_bag[i >> 5] |= 1u << (i & 31); s_mul[i >> 5] |= 1u << (i & 31); ++left; }
+    }
+    rand_state[blk] = x;
+    atomicAdd(count, left);
+  }
+  __syncthreads();
+  const float multiply = static_cast<float>(cnt - top_k) / other_k;
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    if ((s_mul[i >> 5] >> (i & 31)) & 1u) {
+      for (int k = 0; k < K; ++k) {
+        const size_t idx = static_cast<size_t>(k) * n + start + i;
+        grad[idx] *= multiply; hess[idx] *= multiply;
+      }
+    }
+  }
+  if (threadIdx.x < 32) bits[blk * 32 + threadIdx.x] = s_bag[threadIdx.x];
+}
+// every row in the bag (GOSS's first 1 / learning_rate iterations)
+__global__ void k_bag_all(unsigned int* __restrict__ bits, int n) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nw = (n + 31) / 32;
+  if (w >= ((n + 1023) / 1024) * 32) return;
+  unsigned int v = 0u;
+  if (w < nw) v = (w == nw - 1 && (n & 31)) ? ((1u << (n & 31)) - 1u) : 0xffffffffu;
+  bits[w] = v;
+}
+// score = (score * pre + v) * post for every row (a random forest's constant tree entering the running mean)
+__global__ void k_mix_constant(double* p, long long n, double pre, double v, double post) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    p[i] = (p[i] * pre + v) * post;
+}
+__global__ void k_fill_double(double* p, long long n, double v) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) p[i] = v;
+}
+
 // ------------------------------------------------------------------------------------------------ K8 + K3 fused
 // Applies the finished tree to the training scores by walking it with every row's bins (row-major records, streamed once)
 // instead of going through the leaves' index ranges, and — for the row-wise objectives — computes the next iteration's
@@ -1022,21 +1101,35 @@ __global__ void __launch_bounds__(256) k_bt_select(NodeDev* __restrict__ nodes, 
 constexpr int kApplyThreads = 256;
 constexpr int kApplyMaxFeatures = 1 << 14;      // node word: feature (14 bits) | nan bin (9) | threshold (8) | default_left (1)
 
+// ScoreMix: score = (score * pre + leaf) * post.  Gradient boosting uses (1, 1); a random forest keeps the running mean of its
+// trees in the scores (pre = iterations so far, post = 1 / (iterations + 1): RF::TrainOneIter's MultiplyScore / UpdateScore /
+// MultiplyScore).  bias: added to every leaf value before it is used (RF: the tree carries the initial score; Tree::AddBias).
+// shrink != 0: the leaf values are multiplied by lr with Tree::Shrinkage's round-to-zero.
+// (struct ScoreMix: booster.h)
+// ctrl == nullptr: an explicit tree of nl_explicit leaves whose arrays the host uploaded (DART re-adds earlier trees); otherwise
+// the tree the learner has just finished (ctrl->done), once (ctrl->applied).
 template <int OBJ, int WPR>
 __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* __restrict__ rm, unsigned rm_stride,
                                                                  double* __restrict__ score, const float* __restrict__ label,
                                                                  const float* __restrict__ weight, float* __restrict__ grad,
                                                                  float* __restrict__ hess, TreeArraysDev T,
                                                                  const FeatureMetaDev* __restrict__ fmeta, BatchCtrl* __restrict__ ctrl,
-                                                                 double lr, int n, double sigmoid, double lw_neg, double lw_pos) {
+                                                                 double lr, int n, double sigmoid, double lw_neg, double lw_pos,
+                                                                 ScoreMix mix, int nl_explicit) {
   __shared__ double s_val[1024];
   __shared__ uint2 s_node[1024];
-  const int nl = ctrl->num_leaves;
-  if (!ctrl->done || ctrl->abort || ctrl->applied || nl <= 1) return;
+  int nl;
+  if (ctrl != nullptr) {
+    nl = ctrl->num_leaves;
+    if (!ctrl->done || ctrl->abort || ctrl->applied || nl <= 1) return;
+  } else {
+    nl = nl_explicit;
+  }
   for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-    double v = T.leaf_value[i] * lr;
+    double v = T.leaf_value[i];
     const double zt = (double)1e-35f;
-    if (v >= -zt && v <= zt) v = 0.0;
+    if (mix.shrink) { v *= lr; if (v >= -zt && v <= zt) v = 0.0; }
+    if (mix.bias != 0.0) { v += mix.bias; if (v >= -zt && v <= zt) v = 0.0; }
     s_val[i] = v;
     if (i < nl - 1) {
       const int f = T.split_feature_inner[i];
@@ -1066,8 +1159,8 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       }
     }
     const double sc0 = score[row];
-    int node = 0;
-    do {
+    int node = nl > 1 ? 0 : -1;      // a single-leaf tree (explicit trees only): every row is in leaf 0
+    if (node >= 0) do {
       const uint2 nd = s_node[node];
       const int f = nd.x & 0x3fffu;
       const unsigned nan_bin = (nd.x >> 14) & 0x1ffu, thr = (nd.x >> 23) & 0xffu;
@@ -1075,7 +1168,7 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const bool left = (bin == nan_bin) ? ((nd.x >> 31) != 0) : (bin <= thr);
       node = left ? static_cast<int>(static_cast<short>(nd.y & 0xffffu)) : static_cast<int>(static_cast<short>(nd.y >> 16));
     } while (node >= 0);
-    const double sc = sc0 + s_val[~node];
+    const double sc = (sc0 * mix.pre + s_val[~node]) * mix.post;      // (x * 1.0 + v) * 1.0 == x + v exactly
     score[row] = sc;
     if (OBJ != 0) {
       float g, h;

@@ -52,7 +52,18 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   for (auto& kv : train->cfg.raw)
     if (!cfg_.raw.count(kv.first)) cfg_.raw[kv.first] = kv.second;
   g_verbosity = cfg_.verbosity;
-  LGB_CHECK(cfg_.boosting == "gbdt", "boosting_type=%s is not supported by this library yet (gbdt only)", cfg_.boosting.c_str());
+  LGB_CHECK(cfg_.boosting == "gbdt" || cfg_.boosting == "rf" || cfg_.boosting == "dart" || cfg_.boosting == "goss",
+            "boosting_type=%s is not supported by this library (gbdt, rf, dart, goss)", cfg_.boosting.c_str());
+  boost_ = cfg_.boosting == "rf" ? kRF : cfg_.boosting == "dart" ? kDART : cfg_.boosting == "goss" ? kGOSS : kGBDT;
+  shrinkage_rate_ = boost_ == kRF ? 1.0 : cfg_.learning_rate;
+  drop_rand_ = HostRandom(cfg_.drop_seed);
+  if (boost_ == kRF)
+    LGB_CHECK((cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0) || cfg_.feature_fraction < 1.0,
+              "boosting=rf needs bagging (bagging_freq > 0 and bagging_fraction < 1) or feature_fraction < 1");
+  if (boost_ == kGOSS) {
+    LGB_CHECK(cfg_.top_rate > 0.0 && cfg_.other_rate > 0.0 && cfg_.top_rate + cfg_.other_rate <= 1.0, "goss: top_rate + other_rate must be in (0, 1]");
+    LGB_CHECK(!(cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0), "goss cannot be combined with bagging");
+  }
   LGB_CHECK(cfg_.tree_learner == "serial" || cfg_.tree_learner == "data" || cfg_.tree_learner == "data_parallel",
             "tree_learner=%s is not supported by this library (data_parallel / serial)", cfg_.tree_learner.c_str());
   LGB_CHECK(cfg_.num_leaves >= 2 && cfg_.num_leaves <= 1024, "num_leaves=%d is outside [2, 1024]", cfg_.num_leaves);
@@ -124,6 +135,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   d_grad_[0].Alloc(n_ * K_); d_hess_[0].Alloc(n_ * K_);
   d_grad_[1].Alloc(K_ == 1 ? n_ : 1); d_hess_[1].Alloc(K_ == 1 ? n_ : 1);      // the second pair only serves the fused apply + gradient pass
   if (K_ > 1) fuse_grad_ = false;      // a row's gradients depend on all K scores: one gradient kernel per iteration
+  if (boost_ == kRF || boost_ == kDART) fuse_grad_ = false;      // RF: gradients are taken once; DART: trees leave and re-enter the scores between iterations
   if (const char* env = getenv("LGB_B200_FUSE_GRAD")) fuse_grad_ = atoi(env) != 0 && K_ == 1;
   if (lp_.quantized) d_gh16_.Alloc(n_); else d_ghfix_.Alloc(n_);
   idx_es_ = lp_.quantized ? 2 : 4;      // ints per index entry: {row, g|h} or {row, g, h, -}
@@ -161,7 +173,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     LGB_CUDA(cudaMemcpy(d_ctrl_, &hc, sizeof(hc), cudaMemcpyHostToDevice));
     if (const char* from = getenv("LGB_B200_TRACE_FROM")) trace_from_ = atoi(from);
   }
-  bagging_ = cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0;
+  bagging_ = (cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0) || boost_ == kGOSS;
   if (bagging_) {      // ResetSampleConfig: one LCG stream per block of 1024 local rows, seeded bagging_seed + block
     const int nblk = static_cast<int>((n_ + 1023) / 1024);
     std::vector<unsigned int> seeds(nblk);
@@ -191,6 +203,20 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.leaf_parent = ip + 6 * L; tree_dev_.leaf_depth = ip + 7 * L;
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+  }
+  if (boost_ == kDART) {      // a second set of tree arrays for the earlier trees DART re-adds to the scores
+    d_tree_blob2_.AllocZero(tree_blob_bytes_);
+    h_tree_blob2_.resize(tree_blob_bytes_);
+    const size_t ints = 8 * sizeof(int) * L, floats = RoundUp<size_t>(sizeof(float) * L, 8), dbl = 4 * sizeof(double) * L;
+    unsigned char* b = d_tree_blob2_.p;
+    tree_dev2_.leaf_value = reinterpret_cast<double*>(b); tree_dev2_.leaf_weight = tree_dev2_.leaf_value + L;
+    tree_dev2_.internal_value = tree_dev2_.leaf_weight + L; tree_dev2_.internal_weight = tree_dev2_.internal_value + L;
+    int* ip = reinterpret_cast<int*>(b + dbl);
+    tree_dev2_.left_child = ip; tree_dev2_.right_child = ip + L; tree_dev2_.split_feature_inner = ip + 2 * L;
+    tree_dev2_.threshold_in_bin = ip + 3 * L; tree_dev2_.leaf_count = ip + 4 * L; tree_dev2_.internal_count = ip + 5 * L;
+    tree_dev2_.leaf_parent = ip + 6 * L; tree_dev2_.leaf_depth = ip + 7 * L;
+    tree_dev2_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
+    tree_dev2_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
   }
   SetSmem(k_bt_select, SelectSmemBytes(1024));   // the largest tree the learner accepts; launches ask for what their num_leaves needs
 #define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
@@ -468,23 +494,24 @@ double Booster::BoostFromScoreLocalSums(double* suml, double* sumw) const {
   return 0.0;
 }
 
-void Booster::ComputeGradients() {
+void Booster::ComputeGradients(const double* score_override) {
   const int n = static_cast<int>(n_);
+  const double* score = score_override ? score_override : d_score_.p;
   const int grid = std::min(CeilDiv(n, 256), kNumSms * 8);
   const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
   if (obj_ == kMulticlass) {
-    k_grad_multiclass<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[0].p, d_hess_[0].p, n, K_, static_cast<double>(K_) / (K_ - 1.0f));
+    k_grad_multiclass<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[0].p, d_hess_[0].p, n, K_, static_cast<double>(K_) / (K_ - 1.0f));
   } else if (obj_ == kBinary) {
-    k_grad_binary<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
+    k_grad_binary<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
-    k_grad_l2<<<grid, 256, 0, stream_>>>(d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
+    k_grad_l2<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
   } else if (obj_ >= kHuber) {
     const double p0 = obj_ == kHuber ? cfg_.alpha : obj_ == kFair ? cfg_.fair_c : obj_ == kPoisson ? SoftExp(cfg_.poisson_max_delta_step)
                       : cfg_.tweedie_variance_power;
-    k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), d_score_.p, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0);
+    k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0);
   } else {
     LambdarankArgs a;
-    a.score = d_score_.p; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
+    a.score = score; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
     a.inv_max_dcg = d_inv_max_dcg_.p; a.label_gain = d_label_gain_.p; a.discount = d_discount_.p; a.sigmoid_table = d_sigmoid_table_.p;
     a.grad = d_grad_[grad_cur_].p; a.hess = d_hess_[grad_cur_].p; a.sigmoid = cfg_.sigmoid; a.min_sigmoid_input = min_sigmoid_input_;
     a.max_sigmoid_input = max_sigmoid_input_; a.idx_factor = sigmoid_table_idx_factor_;
@@ -641,6 +668,7 @@ void Booster::EnqueueRounds(int rounds) {
 // BaggingSampleStrategy::Bagging: a new bag at every iteration that is a multiple of bagging_freq (each rank over its own rows).
 // The root's row count is the number of rows in the bags of all ranks.
 void Booster::Bagging() {
+  if (boost_ == kGOSS) { GossSample(); return; }
   if (!bagging_ || iter_ % cfg_.bagging_freq != 0) return;
   const int n = static_cast<int>(n_);
   LGB_CUDA(cudaMemsetAsync(d_bag_count_.p, 0, sizeof(int), stream_));
@@ -654,6 +682,128 @@ void Booster::Bagging() {
   net_->HostAllGatherInt64(local, &all);
   bag_cnt_global_ = 0;
   for (long long c : all) bag_cnt_global_ += c;
+}
+
+// GOSS (upstream src/boosting/goss.hpp): from iteration 1 / learning_rate on, every 1024-row block keeps its top_rate rows by
+// |g * h| and a random other_rate of the rest with scaled-up gradients (k_goss_sample); before that every row is in the bag.
+void Booster::GossSample() {
+  const int n = static_cast<int>(n_);
+  const int nblk = CeilDiv(n, 1024);
+  int local = n;
+  if (iter_ < static_cast<int>(1.0f / cfg_.learning_rate)) {
+    k_bag_all<<<CeilDiv(nblk * 32, 256), 256, 0, stream_>>>(d_bag_bits_.p, n);
+  } else {
+    LGB_CUDA(cudaMemsetAsync(d_bag_count_.p, 0, sizeof(int), stream_));
+    k_goss_sample<<<nblk, 256, 0, stream_>>>(d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, K_, cfg_.top_rate, cfg_.other_rate, d_bag_rand_.p,
+                                             d_bag_bits_.p, d_bag_count_.p);
+    LGB_CUDA(cudaMemcpyAsync(&local, d_bag_count_.p, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+    LGB_CUDA(cudaStreamSynchronize(stream_));
+  }
+  LGB_CUDA(cudaGetLastError());
+  ++launches_;
+  std::vector<long long> all;
+  net_->HostAllGatherInt64(local, &all);
+  bag_cnt_global_ = 0;
+  for (long long c : all) bag_cnt_global_ += c;
+}
+
+// ScoreUpdater::AddScore(tree, class) for an earlier tree: its arrays go to the second device tree and every row walks it.
+void Booster::AddHostTreeToScores(const HostTree& t, int cls, bool train, bool valid) {
+  const int L = cfg_.num_leaves;
+  const int nl = t.num_leaves;
+  LGB_CHECK(nl <= L, "AddHostTreeToScores: the tree has more leaves than num_leaves");
+  LGB_CHECK(nl <= 1 || static_cast<int>(t.split_feature_inner.size()) == nl - 1, "this tree was not trained by this booster (no bin-level splits)");
+  unsigned char* b = h_tree_blob2_.data();
+  const size_t dbl = 4 * sizeof(double) * L, ints = 8 * sizeof(int) * L, floats = RoundUp<size_t>(sizeof(float) * L, 8);
+  double* dv = reinterpret_cast<double*>(b);
+  int* ip = reinterpret_cast<int*>(b + dbl);
+  signed char* cp = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+  for (int i = 0; i < nl; ++i) dv[i] = t.leaf_value[i];
+  for (int i = 0; i < nl - 1; ++i) {
+    ip[i] = t.left_child[i]; ip[L + i] = t.right_child[i]; ip[2 * L + i] = t.split_feature_inner[i]; ip[3 * L + i] = t.threshold_in_bin[i];
+    cp[i] = t.decision_type[i];
+  }
+  LGB_CUDA(cudaMemcpyAsync(d_tree_blob2_.p, b, tree_blob_bytes_, cudaMemcpyHostToDevice, stream_));
+  LGB_CUDA(cudaStreamSynchronize(stream_));      // the host blob is reused by the next tree
+  const ScoreMix plain{1.0, 1.0, 0.0, 0};
+  auto run = [&](const Dataset* d, double* score) {
+    const int n = static_cast<int>(d->num_data);
+    if (n == 0) return;
+    const BinLayout& lay = d->layout;
+    const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
+#define APPLY_P(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), score, \
+        nullptr, nullptr, nullptr, nullptr, tree_dev2_, ds_->d_fmeta.p, static_cast<BatchCtrl*>(nullptr), 1.0, n, cfg_.sigmoid, 1.0, 1.0, plain, nl)
+    if (lay.rm_stride == 32) APPLY_P(8); else if (lay.rm_stride == 64) APPLY_P(16); else APPLY_P(0);
+#undef APPLY_P
+    ++launches_;
+  };
+  if (train) run(ds_, d_score_.p + static_cast<size_t>(cls) * n_);
+  if (valid) for (ValidSet& v : valids_) run(v.ds, v.score.p + static_cast<size_t>(cls) * v.ds->num_data);
+  LGB_CUDA(cudaGetLastError());
+}
+
+// DART::DroppingTrees (upstream src/boosting/dart.hpp): draws the iterations to drop, takes their trees out of the training scores
+// and sets this iteration's shrinkage.
+void Booster::DroppingTrees() {
+  drop_index_.clear();
+  const bool is_skip = drop_rand_.NextFloat() < cfg_.skip_drop;
+  if (!is_skip) {
+    double drop_rate = cfg_.drop_rate;
+    if (!cfg_.uniform_drop) {
+      const double inv_average_weight = static_cast<double>(tree_weight_.size()) / sum_weight_;
+      if (cfg_.max_drop > 0) drop_rate = std::min(drop_rate, cfg_.max_drop * inv_average_weight / sum_weight_);
+      for (int i = 0; i < iter_; ++i) {
+        if (drop_rand_.NextFloat() < drop_rate * tree_weight_[i] * inv_average_weight) {
+          drop_index_.push_back(num_init_iteration_ + i);
+          if (drop_index_.size() >= static_cast<size_t>(cfg_.max_drop)) break;
+        }
+      }
+    } else {
+      if (cfg_.max_drop > 0) drop_rate = std::min(drop_rate, cfg_.max_drop / static_cast<double>(iter_));
+      for (int i = 0; i < iter_; ++i) {
+        if (drop_rand_.NextFloat() < drop_rate) {
+          drop_index_.push_back(num_init_iteration_ + i);
+          if (drop_index_.size() >= static_cast<size_t>(cfg_.max_drop)) break;
+        }
+      }
+    }
+  }
+  for (int i : drop_index_) {
+    for (int k = 0; k < K_; ++k) {
+      HostTree& t = models_[static_cast<size_t>(i) * K_ + k];
+      t.Shrinkage(-1.0);
+      AddHostTreeToScores(t, k, true, false);
+    }
+  }
+  if (!cfg_.xgboost_dart_mode) shrinkage_rate_ = cfg_.learning_rate / (1.0f + static_cast<double>(drop_index_.size()));
+  else if (drop_index_.empty()) shrinkage_rate_ = cfg_.learning_rate;
+  else shrinkage_rate_ = cfg_.learning_rate / (cfg_.learning_rate + static_cast<double>(drop_index_.size()));
+}
+
+// DART::Normalize: the dropped trees come back scaled by k / (k + 1) (xgboost mode: k / (k + learning_rate)); the validation
+// scores, which kept them, lose the difference.
+void Booster::NormalizeDart() {
+  const double k = static_cast<double>(drop_index_.size());
+  for (int i : drop_index_) {
+    for (int c = 0; c < K_; ++c) {
+      HostTree& t = models_[static_cast<size_t>(i) * K_ + c];
+      if (!cfg_.xgboost_dart_mode) t.Shrinkage(1.0f / (k + 1.0f)); else t.Shrinkage(shrinkage_rate_);
+      AddHostTreeToScores(t, c, false, true);
+      if (!cfg_.xgboost_dart_mode) t.Shrinkage(-k); else t.Shrinkage(-k / cfg_.learning_rate);
+      AddHostTreeToScores(t, c, true, false);
+    }
+    if (!cfg_.uniform_drop) {
+      const int w = i - num_init_iteration_;
+      if (!cfg_.xgboost_dart_mode) {
+        sum_weight_ -= tree_weight_[w] * (1.0f / (k + 1.0f));
+        tree_weight_[w] *= (k / (k + 1.0f));
+      } else {
+        sum_weight_ -= tree_weight_[w] * (1.0f / (k + cfg_.learning_rate));
+        tree_weight_[w] *= (k / (k + cfg_.learning_rate));
+      }
+    }
+  }
+  ++model_version_;
 }
 
 void Booster::SampleFeaturesForTree() {
@@ -774,7 +924,7 @@ void Booster::UpdateScores() {
   float* h = d_hess_[grad_cur_ ^ 1].p;
   if (obj != 0) LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
 #define APPLY_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_score_.p + cls_ * n_, ds_->d_label.p, w, g, h, tree_dev_, ds_->d_fmeta.p, d_ctrl_, \
-                   cfg_.learning_rate, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]
+                   shrinkage_rate_, n, cfg_.sigmoid, label_weights_[0], label_weights_[1], mix_, 0
 #define APPLY(OBJ)                                                                                              \
   do {                                                                                                          \
     if (lay.rm_stride == 32) k_bt_apply_tree<OBJ, 8><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);          \
@@ -800,7 +950,7 @@ void Booster::ApplyTreeToValidSets() {
     const BinLayout& lay = d->layout;
     const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
 #define APPLY_V(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p + cls_ * d->num_data, \
-        nullptr, nullptr, nullptr, nullptr, tree_dev_, ds_->d_fmeta.p, d_ctrl_, cfg_.learning_rate, n, cfg_.sigmoid, 1.0, 1.0)
+        nullptr, nullptr, nullptr, nullptr, tree_dev_, ds_->d_fmeta.p, d_ctrl_, shrinkage_rate_, n, cfg_.sigmoid, 1.0, 1.0, mix_, 0)
     if (lay.rm_stride == 32) APPLY_V(8); else if (lay.rm_stride == 64) APPLY_V(16); else APPLY_V(0);
 #undef APPLY_V
     ++launches_;
@@ -868,9 +1018,31 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     AddConstantToValidSets(v);
     ++launches_;
   };
+  const long long iter_total = iter_ + num_init_iteration_;
+  if (boost_ == kRF) {
+    LGB_CHECK(!custom, "LGBM_BoosterUpdateOneIterCustom with boosting=rf is not supported by this library");
+    // RF::Boosting: the automatic initial scores are not added to the scores (every tree carries them); the gradients are taken
+    // once, at those constant scores
+    if (rf_init_scores_.empty()) {
+      rf_init_scores_.assign(K_, 0.0);
+      for (cls_ = 0; cls_ < K_; ++cls_) {
+        if (!ds_->has_init_score && (cfg_.boost_from_average || F_ == 0)) {
+          const double v = automatic_init_score();
+          if (std::fabs(v) > kEps) rf_init_scores_[cls_] = v;
+        }
+      }
+      cls_ = 0;
+      DevBuf<double> tmp;
+      tmp.Alloc(static_cast<size_t>(n_) * K_);
+      for (int k = 0; k < K_; ++k)
+        k_fill_double<<<std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8), 256, 0, stream_>>>(tmp.p + static_cast<size_t>(k) * n_, n_, rf_init_scores_[k]);
+      ComputeGradients(tmp.p);
+      LGB_CUDA(cudaStreamSynchronize(stream_));
+    }
+  }
   // GBDT::BoostFromAverage, once per class
   std::vector<double> init_scores(K_, 0.0);
-  if (!custom && models_.empty() && !ds_->has_init_score && (cfg_.boost_from_average || F_ == 0)) {
+  if (boost_ != kRF && !custom && models_.empty() && !ds_->has_init_score && (cfg_.boost_from_average || F_ == 0)) {
     for (cls_ = 0; cls_ < K_; ++cls_) {
       const double v = automatic_init_score();
       if (std::fabs(v) > kEps) {
@@ -881,6 +1053,7 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     }
     cls_ = 0;
   }
+  if (boost_ == kDART) DroppingTrees();      // DART::GetTrainingScore: before the gradients are taken
   // Boosting(): the gradients of all classes from the scores before this iteration's trees
   const bool any_train = K_ > 1 ? std::any_of(class_need_train_.begin(), class_need_train_.end(), [](char c) { return c != 0; }) : need_train_;
   const bool fused = grad_ready_ && !custom;       // produced by the previous iteration's apply-tree pass
@@ -889,7 +1062,7 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     else if (custom) {       // pageable sources are staged before the calls return
       LGB_CUDA(cudaMemcpyAsync(d_grad_[grad_cur_].p, custom_grad, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
       LGB_CUDA(cudaMemcpyAsync(d_hess_[grad_cur_].p, custom_hess, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
-    } else { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
+    } else if (boost_ != kRF) { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
     grad_ready_ = false;
     Bagging();
   }
@@ -900,13 +1073,28 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     tree.leaf_value.assign(1, 0.0);
     const bool train_this = K_ > 1 ? class_need_train_[cls_] != 0 : need_train_;
     if (train_this && F_ > 0) {
-      ProfBegin("quantize"); PrepareGradients(fused); ProfEnd();
+      if (boost_ == kRF)      // the scores keep the running mean of the trees; the tree enters with the initial score as its bias
+        mix_ = ScoreMix{static_cast<double>(iter_total), 1.0 / (iter_total + 1), std::fabs(rf_init_scores_[cls_]) > kEps ? rf_init_scores_[cls_] : 0.0, 0};
+      ProfBegin("quantize"); PrepareGradients(fused && boost_ != kGOSS); ProfEnd();      // GOSS has rescaled gradients: new maxima
       TrainTree(&tree);
       if (tree.num_leaves <= 1) grad_ready_ = false;      // no tree, so the apply pass did nothing
     }
-    if (tree.num_leaves > 1) {
+    if (boost_ == kRF) {
+      if (tree.num_leaves > 1) {
+        if (std::fabs(rf_init_scores_[cls_]) > kEps) tree.AddBias(rf_init_scores_[cls_]);
+      } else if (static_cast<int>(models_.size()) < K_) {
+        double output = rf_init_scores_[cls_];
+        if (!train_this) output = automatic_init_score();      // objective->BoostFromScore(class)
+        tree.AsConstantTree(output);
+        const int grid = std::min(CeilDiv(static_cast<int>(n_), 256), kNumSms * 8);
+        k_mix_constant<<<grid, 256, 0, stream_>>>(d_score_.p + cls_ * n_, n_, static_cast<double>(iter_total), output, 1.0 / (iter_total + 1));
+        for (ValidSet& vs : valids_)
+          k_mix_constant<<<grid, 256, 0, stream_>>>(vs.score.p + cls_ * vs.ds->num_data, vs.ds->num_data, static_cast<double>(iter_total), output, 1.0 / (iter_total + 1));
+      }
+      should_continue = true;      // a forest never stops early
+    } else if (tree.num_leaves > 1) {
       should_continue = true;      // (the scores were advanced inside TrainTree, behind the tree's last round)
-      tree.Shrinkage(cfg_.learning_rate);
+      tree.Shrinkage(shrinkage_rate_);
       if (std::fabs(init_scores[cls_]) > kEps) tree.AddBias(init_scores[cls_]);
     } else if (static_cast<int>(models_.size()) < K_) {
       // "only add default score one-time" (GBDT::TrainOneIter): with boost_from_average the initial score is already in the scores
@@ -939,6 +1127,10 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     return true;
   }
   ++iter_;
+  if (boost_ == kDART) {      // DART::TrainOneIter, after GBDT::TrainOneIter
+    NormalizeDart();
+    if (!cfg_.uniform_drop) { tree_weight_.push_back(shrinkage_rate_); sum_weight_ += shrinkage_rate_; }
+  }
   return false;
 }
 
@@ -952,6 +1144,7 @@ ModelHeader Booster::MakeHeader() const {
   else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
   else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
+  h.average_output = boost_ == kRF;
   h.feature_names = ds_->feature_names;
   for (int j = 0; j < ds_->num_total_features; ++j) {
     const BinMapperH& m = ds_->mappers[j];
@@ -1019,6 +1212,7 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
             "Model string: num_class=%d / num_tree_per_iteration=%d do not fit objective '%s'", loaded_header_.num_class,
             loaded_header_.num_tree_per_iteration, o.c_str());
   LGB_CHECK(models_.size() % K_ == 0, "Model string: %d trees are not a multiple of num_tree_per_iteration", static_cast<int>(models_.size()));
+  if (loaded_header_.average_output) boost_ = kRF;
   device_ = -1;      // resolved at the first prediction: loading and re-saving a model needs no GPU
   iter_ = static_cast<int>(models_.size()) / K_;
   model_version_ = 1;
@@ -1127,10 +1321,10 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
     const long long rs = row_major ? ncol : 1, cs = row_major ? 1 : nr;
     const int grid = static_cast<int>(std::min<int64_t>(CeilDiv(static_cast<int>(std::min<int64_t>(nr, 1 << 30)), 128), kNumSms * 16));
     if (data_type == 1)
-      k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, predict_type, sig_on,
+      k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, boost_ == kRF ? (t1 - t0) / K_ : 0, predict_type, sig_on,
                                                    cfg_.sigmoid, dp_out_.p);
     else
-      k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, predict_type, sig_on,
+      k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, boost_ == kRF ? (t1 - t0) / K_ : 0, predict_type, sig_on,
                                                   cfg_.sigmoid, dp_out_.p);
     LGB_CUDA(cudaGetLastError());
     LGB_CUDA(cudaMemcpyAsync(out + static_cast<size_t>(r0) * per_row, dp_out_.p, sizeof(double) * nr * per_row, cudaMemcpyDeviceToHost, stream_));

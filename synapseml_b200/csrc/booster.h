@@ -83,6 +83,9 @@ struct TreeCtrl {
   long long hist_rows, hist_launches;
 };
 
+// how a finished tree enters the scores (k_bt_apply_tree, batch_tree.cuh)
+struct ScoreMix { double pre, post, bias; int shrink; };
+
 struct TreeArraysDev {
   int *left_child, *right_child, *split_feature_inner, *threshold_in_bin, *leaf_count, *internal_count, *leaf_parent, *leaf_depth;
   signed char* decision_type;
@@ -169,6 +172,23 @@ class Booster {
   int iter_ = 0;
   enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass } obj_ = kL2;
   bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie); }
+  // boosting type (upstream src/boosting/{gbdt,rf,dart,goss}.hpp)
+  enum Boost { kGBDT, kRF, kDART, kGOSS } boost_ = kGBDT;
+  double shrinkage_rate_ = 0.1;             // learning_rate; DART rescales it by the number of dropped trees, RF uses 1
+  ScoreMix mix_{1.0, 1.0, 0.0, 1};          // how the finished tree enters the scores (batch_tree.cuh)
+  std::vector<double> rf_init_scores_;      // RF: the automatic initial scores; every tree carries them as a bias
+  HostRandom drop_rand_{4};                 // DART: random_for_drop_
+  std::vector<double> tree_weight_;
+  double sum_weight_ = 0.0;
+  std::vector<int> drop_index_;
+  void DroppingTrees();
+  void NormalizeDart();
+  void GossSample();
+  // adds an earlier tree (host copy, current leaf values) to the scores of class cls: DART takes trees out and puts them back
+  void AddHostTreeToScores(const HostTree& t, int cls, bool train, bool valid);
+  DevBuf<unsigned char> d_tree_blob2_;
+  TreeArraysDev tree_dev2_{};
+  std::vector<unsigned char> h_tree_blob2_;
   // multiclass: K_ trees per iteration, one per class; scores / gradients are class-major [K_][n_]; cls_ = the class whose tree is being trained
   int K_ = 1, cls_ = 0;
   std::vector<double> class_init_probs_;
@@ -289,7 +309,7 @@ class Booster {
 
   void InitObjective();
   double BoostFromScoreLocalSums(double* suml, double* sumw) const;
-  void ComputeGradients();
+  void ComputeGradients(const double* score_override = nullptr);
   void PrepareGradients(bool absmax_ready);           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);

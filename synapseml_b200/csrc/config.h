@@ -54,6 +54,10 @@ struct Config {
   int feature_fraction_seed = 2;
   double bagging_fraction = 1.0, pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;
   int bagging_freq = 0, bagging_seed = 3;
+  // boosting = dart / goss (upstream config.h defaults)
+  double drop_rate = 0.1, skip_drop = 0.5, top_rate = 0.2, other_rate = 0.1;
+  int max_drop = 50, drop_seed = 4;
+  bool uniform_drop = false, xgboost_dart_mode = false;
   int num_machines = 1;
   int num_threads = 0;
   int verbosity = 1;

@@ -102,6 +102,7 @@ std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& tre
   std::string s = "tree\nversion=v3\nnum_class=" + std::to_string(h.num_class) + "\nnum_tree_per_iteration=" + std::to_string(tpi) + "\nlabel_index=0\n";
   s += "max_feature_idx=" + std::to_string(h.max_feature_idx) + "\n";
   if (!h.objective.empty()) s += "objective=" + h.objective + "\n";
+  if (h.average_output) s += "average_output\n";
   s += "feature_names=";
   for (size_t j = 0; j < h.feature_names.size(); ++j) { if (j) s.push_back(' '); s += h.feature_names[j]; }
   s += "\nfeature_infos=";
@@ -217,6 +218,7 @@ void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostT
       continue;
     }
     if (line == "tree") { saw_tree_word = true; continue; }
+    if (line == "average_output" && !in_tree) { h->average_output = true; continue; }
     if (line == "end of trees") { finish_tree(); continue; }
     if (line == "parameters:") { finish_tree(); in_params = true; continue; }
     if (line == "feature_importances:" || line.rfind("pandas_categorical", 0) == 0) { finish_tree(); continue; }
@@ -283,7 +285,7 @@ std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees
                   std::to_string(tpi) + ",\n\"label_index\":0,\n";
   s += "\"max_feature_idx\":" + std::to_string(h.max_feature_idx) + ",\n";
   if (!h.objective.empty()) s += "\"objective\":\"" + JsonEscape(h.objective) + "\",\n";
-  s += "\"average_output\":false,\n\"feature_names\":[";
+  s += std::string("\"average_output\":") + (h.average_output ? "true" : "false") + ",\n\"feature_names\":[";
   for (size_t j = 0; j < h.feature_names.size(); ++j) { if (j) s += ","; s += "\"" + JsonEscape(h.feature_names[j]) + "\""; }
   s += "],\n\"monotone_constraints\":[],\n\"feature_infos\":{";
   bool first_obj = true;

@@ -28,6 +28,7 @@ struct HostTree {
 
 struct ModelHeader {
   int max_feature_idx = 0;
+  bool average_output = false;                          // boosting=rf: a prediction is the mean of the iterations' trees
   int num_class = 1, num_tree_per_iteration = 1;      // multiclass: one tree per class and iteration, class k's trees are k, k + K, ...
   std::string objective;
   std::vector<std::string> feature_names;

@@ -30,9 +30,10 @@ constexpr int kPredictRaw = 1, kPredictNormal = 0, kPredictLeaf = 2;
 // Trees [t0, t1) of a model with K trees per iteration (tree t belongs to class t % K; t0 and t1 are multiples of K).
 // out: raw / normal: [nrow][K]; leaf index: [nrow][t1 - t0].  Normal output: sigmoid_on 1 = sigmoid, 2 = exp (log-link regression),
 // 3 = softmax over the row's K raw scores (Common::Softmax: subtract the maximum, exp, divide by the sum).
+// average_over > 0: the model averages its iterations (boosting=rf): raw scores are divided by the number of iterations used.
 template <typename T>
 __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long row_stride, long long col_stride, PredModelDev m, int t0,
-                          int t1, int K, int mode, int sigmoid_on, double sigmoid, double* __restrict__ out) {
+                          int t1, int K, int average_over, int mode, int sigmoid_on, double sigmoid, double* __restrict__ out) {
   const double kZero = (double)1e-35f;
   for (long long r = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; r < nrow; r += static_cast<long long>(gridDim.x) * blockDim.x) {
     const T* row = rows + r * row_stride;
@@ -61,6 +62,7 @@ __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long 
         else acc += m.leaf_value[lo + leaf];
       }
       if (mode != kPredictLeaf) {
+        if (average_over > 0) acc /= average_over;      // average_output (random forest): the mean over the iterations used
         if (mode == kPredictNormal && sigmoid_on == 1) acc = 1.0 / (1.0 + SoftExp(-sigmoid * acc));
         else if (mode == kPredictNormal && sigmoid_on == 2) acc = SoftExp(acc);      // log-link regression objectives
         out[r * K + cls] = acc;

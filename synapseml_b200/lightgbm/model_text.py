@@ -55,6 +55,7 @@ class TextTree:
 class TextModel:
     def __init__(self, model_str):
         self.header = {}
+        self.average_output = False
         self.trees = []
         self.parameters = {}
         blocks = model_str.split("\n\n")
@@ -67,6 +68,7 @@ class TextModel:
                 self.trees.append(TextTree(kv))
             elif lines[0] == "tree":
                 self.header = dict(l.split("=", 1) for l in lines[1:] if "=" in l)
+                self.average_output = "average_output" in lines      # boosting=rf: predictions are the mean of the iterations' trees
             elif lines[0] == "parameters:":
                 for l in lines[1:]:
                     if l.startswith("[") and ": " in l:
@@ -86,6 +88,8 @@ class TextModel:
         trees = self.trees if num_iteration is None else self.trees[:num_iteration * K]
         for i, t in enumerate(trees):
             out[:, i % K] += t.predict(X)
+        if self.average_output and trees:
+            out /= len(trees) // K
         return out[:, 0] if K == 1 else out
 
     def predict(self, X):
