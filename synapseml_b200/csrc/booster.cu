@@ -1261,21 +1261,43 @@ void Booster::TreeRange(int start_iteration, int num_iteration, int* t0, int* t1
 int64_t Booster::CalcNumPredict(int64_t nrow, int predict_type, int start_iteration, int num_iteration) const {
   int t0, t1;
   TreeRange(start_iteration, num_iteration, &t0, &t1);
+  if (predict_type == kPredictContrib) return nrow * K_ * (NumTotalFeatures() + 1);
   return predict_type == kPredictLeaf ? nrow * (t1 - t0) : nrow * K_;
 }
 
 void Booster::UploadModel() {
   if (uploaded_version_ == model_version_) return;
-  std::vector<int> node_off(1, 0), leaf_off(1, 0), feat, left, right;
-  std::vector<double> thr, leaf;
+  std::vector<int> node_off(1, 0), leaf_off(1, 0), feat, left, right, icount, lcount, depth;
+  std::vector<double> thr, leaf, expected;
   std::vector<signed char> dt;
+  model_max_depth_ = 0;
   for (const HostTree& t : models_) {
     const int ni = t.num_leaves - 1;
+    const bool has_counts = static_cast<int>(t.internal_count.size()) == ni && static_cast<int>(t.leaf_count.size()) == t.num_leaves;
     for (int i = 0; i < ni; ++i) {
       feat.push_back(t.split_feature[i]); thr.push_back(t.threshold[i]); dt.push_back(t.decision_type[i]);
       left.push_back(t.left_child[i]); right.push_back(t.right_child[i]);
+      icount.push_back(has_counts ? t.internal_count[i] : 0);
     }
-    for (int i = 0; i < t.num_leaves; ++i) leaf.push_back(t.leaf_value[i]);
+    for (int i = 0; i < t.num_leaves; ++i) { leaf.push_back(t.leaf_value[i]); lcount.push_back(has_counts ? t.leaf_count[i] : 0); }
+    // Tree::ExpectedValue and the depth TreeSHAP's path storage is sized for
+    double ev = t.leaf_value[0];
+    int md = 0;
+    if (ni > 0) {
+      ev = 0.0;
+      const double total = has_counts ? static_cast<double>(t.internal_count[0]) : 1.0;
+      for (int i = 0; i < t.num_leaves; ++i) ev += ((has_counts ? t.leaf_count[i] : 0) / total) * t.leaf_value[i];
+      std::vector<std::pair<int, int>> stack(1, {0, 0});
+      while (!stack.empty()) {
+        auto [nd, d] = stack.back();
+        stack.pop_back();
+        if (nd < 0) { md = std::max(md, d); continue; }
+        stack.push_back({t.left_child[nd], d + 1});
+        stack.push_back({t.right_child[nd], d + 1});
+      }
+    }
+    expected.push_back(ev); depth.push_back(md);
+    model_max_depth_ = std::max(model_max_depth_, md);
     node_off.push_back(static_cast<int>(feat.size()));
     leaf_off.push_back(static_cast<int>(leaf.size()));
   }
@@ -1284,7 +1306,7 @@ void Booster::UploadModel() {
     if (!v.empty()) LGB_CUDA(cudaMemcpyAsync(buf.p, v.data(), sizeof(v[0]) * v.size(), cudaMemcpyHostToDevice, stream_));
   };
   up(dp_node_off_, node_off); up(dp_leaf_off_, leaf_off); up(dp_feat_, feat); up(dp_left_, left); up(dp_right_, right);
-  up(dp_thr_, thr); up(dp_leaf_, leaf); up(dp_dt_, dt);
+  up(dp_thr_, thr); up(dp_leaf_, leaf); up(dp_dt_, dt); up(dp_icount_, icount); up(dp_lcount_, lcount); up(dp_expected_, expected); up(dp_depth_, depth);
   LGB_CUDA(cudaStreamSynchronize(stream_));      // the host vectors go out of scope
   uploaded_version_ = model_version_;
 }
@@ -1292,8 +1314,8 @@ void Booster::UploadModel() {
 void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int ncol, bool row_major, int predict_type,
                             int start_iteration, int num_iteration, double* out, int64_t* out_len) {
   LGB_CHECK(data_type == 0 || data_type == 1, "Predict: data_type must be C_API_DTYPE_FLOAT32 or FLOAT64");
-  LGB_CHECK(predict_type == kPredictNormal || predict_type == kPredictRaw || predict_type == kPredictLeaf,
-            "Predict: predict_type %d (feature contributions) is not supported by this library yet", predict_type);
+  LGB_CHECK(predict_type == kPredictNormal || predict_type == kPredictRaw || predict_type == kPredictLeaf || predict_type == kPredictContrib,
+            "Predict: unknown predict_type %d", predict_type);
   LGB_CHECK(ncol == NumTotalFeatures(), "Predict: expected %d columns, got %d", NumTotalFeatures(), ncol);
   LGB_CHECK(nrow >= 0, "Predict: negative row count");
   std::lock_guard<std::mutex> lock(predict_mu_);
@@ -1302,12 +1324,27 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   UploadModel();
   int t0, t1;
   TreeRange(start_iteration, num_iteration, &t0, &t1);
-  const int per_row = predict_type == kPredictLeaf ? (t1 - t0) : K_;
+  const int per_row = predict_type == kPredictLeaf ? (t1 - t0) : predict_type == kPredictContrib ? K_ * (ncol + 1) : K_;
   if (out_len) *out_len = nrow * per_row;
   if (nrow == 0 || per_row == 0) return;
   PredModelDev m;
   m.node_off = dp_node_off_.p; m.leaf_off = dp_leaf_off_.p; m.split_feature = dp_feat_.p; m.threshold = dp_thr_.p;
   m.decision_type = dp_dt_.p; m.left = dp_left_.p; m.right = dp_right_.p; m.leaf_value = dp_leaf_.p;
+  m.internal_count = dp_icount_.p; m.leaf_count = dp_lcount_.p; m.expected = dp_expected_.p; m.max_depth = dp_depth_.p;
+  // feature contributions: TreeSHAP recurses to the depth of the deepest tree and keeps (D + 1)(D + 2) / 2 path elements per thread
+  const int shap_threads = kNumSms * 2 * 128;
+  const int path_elems = (model_max_depth_ + 1) * (model_max_depth_ + 2) / 2;
+  if (predict_type == kPredictContrib) {
+    for (int t = t0; t < t1; ++t)
+      LGB_CHECK(models_[t].num_leaves <= 1 || (static_cast<int>(models_[t].internal_count.size()) == models_[t].num_leaves - 1 && models_[t].internal_count[0] > 0),
+                "feature contributions need the trees' data counts (internal_count / leaf_count), which tree %d lacks", t);
+    dp_paths_.Reserve(static_cast<size_t>(shap_threads) * path_elems * sizeof(ShapPathElement));
+    static bool stack_set = false;
+    size_t need = 2048 + static_cast<size_t>(model_max_depth_ + 2) * 256;
+    size_t cur = 0;
+    LGB_CUDA(cudaDeviceGetLimit(&cur, cudaLimitStackSize));
+    if (!stack_set || cur < need) { LGB_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, std::max(cur, need))); stack_set = true; }
+  }
   const size_t esz = data_type == 1 ? sizeof(double) : sizeof(float);
   // row-major input is processed in chunks of rows; column-major input in one piece
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
@@ -1320,7 +1357,17 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
     LGB_CUDA(cudaMemcpyAsync(dp_in_.p, src, static_cast<size_t>(nr) * ncol * esz, cudaMemcpyHostToDevice, stream_));
     const long long rs = row_major ? ncol : 1, cs = row_major ? 1 : nr;
     const int grid = static_cast<int>(std::min<int64_t>(CeilDiv(static_cast<int>(std::min<int64_t>(nr, 1 << 30)), 128), kNumSms * 16));
-    if (data_type == 1)
+    if (predict_type == kPredictContrib) {
+      LGB_CUDA(cudaMemsetAsync(dp_out_.p, 0, sizeof(double) * nr * per_row, stream_));
+      const int sgrid = std::min(grid, shap_threads / 128);
+      const int avg = boost_ == kRF ? (t1 - t0) / K_ : 0;
+      if (data_type == 1)
+        k_predict_contrib<double><<<sgrid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, ncol, avg,
+                                                              reinterpret_cast<ShapPathElement*>(dp_paths_.p), path_elems, dp_out_.p);
+      else
+        k_predict_contrib<float><<<sgrid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, ncol, avg,
+                                                             reinterpret_cast<ShapPathElement*>(dp_paths_.p), path_elems, dp_out_.p);
+    } else if (data_type == 1)
       k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, boost_ == kRF ? (t1 - t0) / K_ : 0, predict_type, sig_on,
                                                    cfg_.sigmoid, dp_out_.p);
     else

@@ -203,7 +203,10 @@ class Booster {
   bool predict_only_ = false;
   ModelHeader loaded_header_;
   long long model_version_ = 0, uploaded_version_ = -1;
-  DevBuf<int> dp_node_off_, dp_leaf_off_, dp_feat_, dp_left_, dp_right_;
+  DevBuf<int> dp_node_off_, dp_leaf_off_, dp_feat_, dp_left_, dp_right_, dp_icount_, dp_lcount_, dp_depth_;
+  DevBuf<double> dp_expected_;
+  DevBuf<unsigned char> dp_paths_;         // feature contributions: the threads' TreeSHAP paths
+  int model_max_depth_ = 0;
   DevBuf<double> dp_thr_, dp_leaf_, dp_out_;
   DevBuf<signed char> dp_dt_;
   DevBuf<unsigned char> dp_in_;

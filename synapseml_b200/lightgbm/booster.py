@@ -28,7 +28,7 @@ class LightGBMBooster:
             self.num_iterations = n_iter.value
 
     # predict_type constants of the C API (C_API_PREDICT_NORMAL / RAW_SCORE / LEAF_INDEX)
-    PREDICT_NORMAL, PREDICT_RAW, PREDICT_LEAF = 0, 1, 2
+    PREDICT_NORMAL, PREDICT_RAW, PREDICT_LEAF, PREDICT_CONTRIB = 0, 1, 2, 3
 
     def predict_for_mat(self, features, predict_type=0, start_iteration=0, num_iteration=-1):
         """Batch scoring on the GPU: one LGBM_BoosterPredictForMat call for all rows."""
@@ -46,7 +46,7 @@ class LightGBMBooster:
                                                C.c_int(1), C.c_int(predict_type), C.c_int(start_iteration), C.c_int(num_iteration),
                                                b"", C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
         out = out[:out_len.value]
-        return out.reshape(n, -1) if predict_type == self.PREDICT_LEAF else out
+        return out.reshape(n, -1) if predict_type in (self.PREDICT_LEAF, self.PREDICT_CONTRIB) else out
 
     def score(self, row, raw=False):
         """score (:407-427 -> predictForMat :520-557): one row through LGBM_BoosterPredictForMatSingleRow."""

@@ -298,6 +298,12 @@ class LightGBMModelBase:
     def predict_leaf(self, features):
         return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
 
+    def predict_contrib(self, features):
+        """featuresShapCol (LightGBMBooster.scala:418-427, predict type C_API_PREDICT_CONTRIB): per row, the TreeSHAP contribution of
+        every feature followed by the expected value — [n, numFeatures + 1], or [n, numClasses * (numFeatures + 1)] for multiclass.
+        A row's contributions sum to its raw score."""
+        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_CONTRIB)
+
     def getFeatureImportances(self, importance_type="split"):
         return self._native().get_feature_importances(importance_type)
 

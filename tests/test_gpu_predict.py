@@ -76,13 +76,13 @@ def test_normal_leaf_subrange_layouts_and_single_row(native, trained):
         validate(lib.LGBM_BoosterPredictForMatSingleRow(nb.handle, row.ctypes.data_as(C.c_void_p), 1, X.shape[1], 1, 1, 0, -1, b"", C.byref(n),
                                                         out.ctypes.data_as(C.POINTER(C.c_double))))
         assert n.value == 1 and out[0] == raw[i]
-    # wrong width and unsupported predict type fail loudly
+    # wrong width and an unknown predict type fail loudly
     bad = np.zeros((2, X.shape[1] + 1))
     n = C.c_int64()
     o = np.zeros(2)
     assert lib.LGBM_BoosterPredictForMat(nb.handle, bad.ctypes.data_as(C.c_void_p), 1, 2, bad.shape[1], 1, 1, 0, -1, b"", C.byref(n),
                                          o.ctypes.data_as(C.POINTER(C.c_double))) == -1
-    assert lib.LGBM_BoosterPredictForMat(nb.handle, X.ctypes.data_as(C.c_void_p), 1, 2, X.shape[1], 1, 3, 0, -1, b"", C.byref(n),
+    assert lib.LGBM_BoosterPredictForMat(nb.handle, X.ctypes.data_as(C.c_void_p), 1, 2, X.shape[1], 1, 7, 0, -1, b"", C.byref(n),
                                          o.ctypes.data_as(C.POINTER(C.c_double))) == -1
 
 
