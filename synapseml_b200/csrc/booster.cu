@@ -349,8 +349,9 @@ void Booster::DumpTrace() {
   const int n = std::min(hc.trace_n, trace_cap_);
   std::vector<long long> t(static_cast<size_t>(2) * n);
   LGB_CUDA(cudaMemcpy(t.data(), d_trace_.p, sizeof(long long) * 2 * n, cudaMemcpyDeviceToHost));
-  const char* path = getenv("LGB_B200_TRACE");
-  FILE* f = fopen(path, "w");
+  std::string path = getenv("LGB_B200_TRACE");
+  if (net_ != nullptr && net_->active()) path += ".r" + std::to_string(net_->rank());      // one timeline per rank
+  FILE* f = fopen(path.c_str(), "w");
   if (!f) return;
   for (int i = 0; i < n; ++i) fprintf(f, "%lld %lld\n", t[2 * i], t[2 * i + 1]);
   fclose(f);
