@@ -218,7 +218,7 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
 // mostly idle CTAs; that was 15 us of fixed cost per round.)
 // The body: all kHistThreads threads of a CTA; (cta_x, tile) = the CTA's place in a (row_ctas x tiles) arrangement.  The shared
 // histograms must be zero on entry and are zero again on return.
-struct HistShared { int begin[kMaxBatch], count[kMaxBatch], buf[kMaxBatch]; int chunks[kMaxBatch + 1]; int rpc; };
+struct HistShared { int begin[kMaxBatch], count[kMaxBatch], buf[kMaxBatch]; int chunks[kMaxBatch + 1]; int rpc; unsigned long long t_flush; };
 
 template <int R, int BPL, bool FLT, bool ROOT>
 __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __restrict__ gh16,
@@ -272,6 +272,9 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
     sh->chunks[kMaxBatch] = c;
   }
   __syncthreads();
+  LGB_TRACE(ctrl, 23);      // set-up done
+  const bool tracing = c_trace_on != 0 && blockIdx.x == 0 && blockIdx.y == 0;
+  if (tracing && threadIdx.x == 0) sh->t_flush = 0ULL;
   const int total_chunks = sh->chunks[kMaxBatch];
   const int rows_per_cta = sh->rpc;
   for (int chunk = cta_x; chunk < total_chunks; chunk += row_ctas) {      // normally one chunk per CTA
@@ -282,9 +285,14 @@ __device__ __forceinline__ void HistBody(const uint8_t* __restrict__ rm, unsigne
     const int hi = min(count, lo + rows_per_cta);
     const int* idx = ROOT ? nullptr : (buf == 0 ? idx0 : idx1);
     HistRows<R, BPL, FLT, ROOT, !FLT>(rmc, rm_stride, gh16, ghfix, idx, begin, lo, hi, lane_addr, hsm,
-                                      work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask);
+                                      work + static_cast<size_t>(ROOT ? 0 : k) * work_elems, F, tile, rows_per_flush, kmask,
+                                      tracing ? &sh->t_flush : nullptr);
   }
   __syncthreads();      // sh is rewritten by the next call
+  if (tracing && threadIdx.x == 0 && ctrl->trace != nullptr && sh->t_flush != 0ULL) {      // id 24: when CTA 0's (last) flush began
+    const int i = atomicAdd(&ctrl->trace_n, 1);
+    if (i < ctrl->trace_cap) { ctrl->trace[2 * i] = 24; ctrl->trace[2 * i + 1] = static_cast<long long>(sh->t_flush); }
+  }
 }
 
 template <int R, int BPL, bool FLT, bool ROOT>
@@ -328,25 +336,23 @@ k_bt_hist(const uint8_t* __restrict__ rm, unsigned rm_stride, const uint16_t* __
 }
 
 // ------------------------------------------------------------------------------------------------ K5 + K6
-// grid = (F, root ? 1 : 2, batch slots).  CTA (f, c, k): child c of batch item k (c = 0: the freshly built smaller child,
-// c = 1: the larger child = parent - smaller).  The last CTA of each (k, c) reduces the per-feature results to the child's
-// best split.
-// One unit = (feature f, child c, batch slot k), run by a 256-thread sub-block (named barriers, so several can share a CTA).
+// grid = (ceil(features / 8), root ? 1 : 2, batch slots), 256 threads: WARP w of CTA (x, c, k) is the unit (feature 8 x + w, child c,
+// batch item k); c = 0: the freshly built smaller child, c = 1: the larger child = parent - smaller.  A unit loads its feature's
+// bins (summed over the ranks when histograms are exchanged over peer memory), stores the child's histogram in its pool slot and
+// runs the warp-scan split search (WarpFindBest, kernels.cuh).  With few features (LearnerParams::reduce_in_select) the replay
+// kernel picks each child's best feature; otherwise the unit that finishes last for a child reduces over the (rank's) features.
+constexpr int kFindWarps = 8;
+
 template <bool QUANT>
-__device__ __forceinline__ void FindUnit(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
-                                         NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
-                                         const LearnerParams& P, int root, int f, int c, int k, int sub, const PeerTable* pt = nullptr) {
-  __shared__ int s_last_all[kMaxFindSubs];
-  __shared__ double s_gain_all[kMaxFindSubs][8];
-  __shared__ int s_feat_all[kMaxFindSubs][8], s_idx_all[kMaxFindSubs][8];
-  int& s_last = s_last_all[sub];
-  double* s_gain = s_gain_all[sub]; int* s_feat = s_feat_all[sub]; int* s_idx = s_idx_all[sub];
+__device__ __forceinline__ void FindUnitWarp(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
+                                             NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
+                                             const LearnerParams& P, int root, int f, int c, int k, const PeerTable& pt) {
   const int F = P.num_features;
-  const int b = threadIdx.x & (kFindThreads - 1);
+  const int lane = threadIdx.x & 31;
   // feature-sliced exchange: this rank owns features [f_first, f_first + nf) and sends the best of them to every rank
-  const bool sliced = pt != nullptr && pt->world > 0 && pt->sliced != 0;
-  const int f_first = sliced ? pt->f_lo : 0;
-  const int nf = sliced ? pt->f_hi - pt->f_lo : F;
+  const bool sliced = pt.world > 0 && pt.sliced != 0;
+  const int f_first = sliced ? pt.f_lo : 0;
+  const int nf = sliced ? pt.f_hi - pt.f_lo : F;
   // ---- which node is this, and what do we know about it
   NodeDev me;              // what gets published for the child (root: only the fields the search needs)
   int node, parent = -1, parent_slot = 0, side = 0;
@@ -376,7 +382,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   me.child_feat[0] = me.child_feat[1] = -1; me.child_count[0] = me.child_count[1] = 0; me.child_gain[0] = me.child_gain[1] = KMINSCORE;
   if (!find) {         // children that are not searched are published by their first unit alone
     if (f != f_first) return;
-    if (b == 0) {
+    if (lane == 0) {
       me.best = EmptySplit(-1, -1);
       nodes[node] = me;
       nodes[parent].child_gain[side] = KMINSCORE; nodes[parent].child_feat[side] = -1; nodes[parent].child_count[side] = me.global_count;
@@ -387,34 +393,55 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   const FeatureMetaDev fm = fmeta[f];
   const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
   const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
-  const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
-  longlong2 v;
   const size_t item_off = static_cast<size_t>(root ? 0 : k) * work_elems;
-  if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
-    long long a = 0, bsum = 0;
-    for (int r = 0; r < pt->world; ++r) {
-      const long long* w = pt->work[r] + pt->parity_off + item_off;
-      if (QUANT) a += w[static_cast<size_t>(f) * kBins + b];
-      else { const longlong2 t = *reinterpret_cast<const longlong2*>(w + off); a += t.x; bsum += t.y; }
+  const size_t bin0 = static_cast<size_t>(f) * kBins + lane * kBinsPerLane;      // the lane's first bin of this feature
+  long long g_in[kBinsPerLane], h_in[kBinsPerLane];
+  if (pt.world > 0) {      // the sum of all ranks' bins, read over peer memory
+    #pragma unroll
+    for (int j = 0; j < kBinsPerLane; ++j) { g_in[j] = 0; h_in[j] = 0; }
+    for (int r = 0; r < pt.world; ++r) {
+      const long long* w = pt.work[r] + pt.parity_off + item_off;
+      if (QUANT) {
+        const longlong2* src = reinterpret_cast<const longlong2*>(w + bin0);
+        #pragma unroll
+        for (int j = 0; j < kBinsPerLane / 2; ++j) { const longlong2 t = src[j]; g_in[2 * j] += t.x; g_in[2 * j + 1] += t.y; }
+      } else {
+        const longlong2* src = reinterpret_cast<const longlong2*>(w + bin0 * 2);
+        #pragma unroll
+        for (int j = 0; j < kBinsPerLane; ++j) { const longlong2 t = src[j]; g_in[j] += t.x; h_in[j] += t.y; }
+      }
     }
-    if (QUANT) { v.y = a & 0xffffffffLL; v.x = (a - v.y) >> 32; }
-    else { v.x = a; v.y = bsum; }
+    if (QUANT) {
+      #pragma unroll
+      for (int j = 0; j < kBinsPerLane; ++j) { const long long a = g_in[j]; h_in[j] = a & 0xffffffffLL; g_in[j] = (a - h_in[j]) >> 32; }
+    }
   } else if (QUANT) {     // packed work area: (sum g << 32) + sum h
-    const long long pk = work[item_off + static_cast<size_t>(f) * kBins + b];
-    v.y = pk & 0xffffffffLL;
-    v.x = (pk - v.y) >> 32;
+    const longlong2* src = reinterpret_cast<const longlong2*>(work + item_off + bin0);
+    #pragma unroll
+    for (int j = 0; j < kBinsPerLane / 2; ++j) {
+      const longlong2 t = src[j];
+      h_in[2 * j] = t.x & 0xffffffffLL; g_in[2 * j] = (t.x - h_in[2 * j]) >> 32;
+      h_in[2 * j + 1] = t.y & 0xffffffffLL; g_in[2 * j + 1] = (t.y - h_in[2 * j + 1]) >> 32;
+    }
   } else {
-    v = *reinterpret_cast<const longlong2*>(work + item_off + off);
+    const longlong2* src = reinterpret_cast<const longlong2*>(work + item_off + bin0 * 2);
+    #pragma unroll
+    for (int j = 0; j < kBinsPerLane; ++j) { const longlong2 t = src[j]; g_in[j] = t.x; h_in[j] = t.y; }
   }
   bool used = true;
   if (!root) {
     used = splittable[static_cast<size_t>(parent) * F + f] != 0;
     if (c == 1) {
-      const longlong2 p = *reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(parent_slot) * slot_stride + off);
-      v.x = p.x - v.x; v.y = p.y - v.y;
+      const longlong2* p = reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(parent_slot) * slot_stride + bin0 * 2);
+      #pragma unroll
+      for (int j = 0; j < kBinsPerLane; ++j) { const longlong2 t = p[j]; g_in[j] = t.x - g_in[j]; h_in[j] = t.y - h_in[j]; }
     }
   }
-  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
+  {
+    longlong2* dst = reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + bin0 * 2);
+    #pragma unroll
+    for (int j = 0; j < kBinsPerLane; ++j) dst[j] = make_longlong2(g_in[j], h_in[j]);
+  }
   SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
   unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
   long long tg = me.int_g, th = me.int_h;
@@ -422,15 +449,15 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   // because the leaf totals come out of it, and its result is discarded.
   const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
   if (!used || (!sampled && !root)) {
-    if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
+    if (lane == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
-    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
-                         fb + f, spl, &tg, &th, sub);
-    if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
+    WarpFindBest<QUANT>(g_in, h_in, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                        fb + f, spl, &tg, &th);
+    if (!sampled && lane == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // lane 0 wrote the result it now replaces
   }
   if (P.reduce_in_select && !sliced) {
     // the replay kernel picks the child's best feature (SelectReduceChildren); the first unit publishes everything else
-    if (f == 0 && b == 0) {
+    if (f == 0 && lane == 0) {
       if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
         me.int_g = tg; me.int_h = th;
         me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
@@ -442,70 +469,60 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
       N.child_feat[0] = N.child_feat[1] = -1; N.child_count[0] = N.child_count[1] = 0;
       N.child_gain[0] = N.child_gain[1] = KMINSCORE;
     }
-    SubSync(sub);
     return;
   }
-  __threadfence();
-  SubSync(sub);
-  if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == nf - 1);
-  SubSync(sub);
-  if (s_last) {       // the last unit of this child reduces over the (rank's) features and publishes the child
+  // the unit that finishes last for this child reduces over the (rank's) features and publishes the child
+  int last = 0;
+  if (lane == 0) {
     __threadfence();
-    double bg = KMINSCORE; int bf = -1, bi = -1;
-    for (int j = f_first + b; j < f_first + nf; j += kFindThreads) {
-      const double g = fb[j].gain; const int rf = fb[j].real_feature;
-      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
-    }
-    const int lane = b & 31, warp = b >> 5;
-    for (int o = 16; o > 0; o >>= 1) {
-      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
-      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
-      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
-    }
-    if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
-    SubSync(sub);
-    if (b == 0) {
-      bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
-      for (int w = 1; w < 8; ++w)
-        if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
-      if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
-        me.int_g = tg; me.int_h = th;
-        me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
-      }
-      if (sliced) {      // the child's best split is chosen by the replay kernel from all ranks' records (SelectReducePeers)
-        me.best = EmptySplit(-1, -1);
-        nodes[node] = me;
-        s_idx[0] = bi;
-      } else {
-        me.best = fb[bi];
-        nodes[node] = me;
-        if (!root) {
-          nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
-          nodes[parent].child_count[side] = me.global_count;
-        }
-      }
-      ctrl->find_count[root ? 0 : k][c] = 0;
-    }
-    if (sliced) {        // thread r stores this rank's record into rank r's mailbox, then stamps it
-      SubSync(sub);
-      if (b < pt->world) {
-        SplitMail* dst = &pt->mail[b]->split[pt->seq & 1u][root ? 0 : (k * 2 + c)][pt->rank];
-        dst->s = fb[s_idx[0]];
-        dst->tot_g = tg; dst->tot_h = th;
-        __threadfence_system();
-        StoreReleaseSys(&dst->seq, pt->seq);
-      }
-    }
+    last = atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == nf - 1;
   }
-  SubSync(sub);       // the sub-block's shared scratch is reused by its next unit
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (!last) return;
+  __threadfence();
+  double bg = KMINSCORE; int bf = -1, bi = -1;
+  for (int j = f_first + lane; j < f_first + nf; j += 32) {
+    const double g = fb[j].gain; const int rf = fb[j].real_feature;
+    if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+    const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+    const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
+  }
+  if (lane == 0) {
+    if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
+      me.int_g = tg; me.int_h = th;
+      me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
+    }
+    if (sliced) {      // the child's best split is chosen by the replay kernel from all ranks' records (SelectReducePeers)
+      me.best = EmptySplit(-1, -1);
+      nodes[node] = me;
+    } else {
+      me.best = fb[bi];
+      nodes[node] = me;
+      if (!root) {
+        nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
+        nodes[parent].child_count[side] = me.global_count;
+      }
+    }
+    ctrl->find_count[root ? 0 : k][c] = 0;
+  }
+  if (sliced && lane < pt.world) {        // lane r stores this rank's record into rank r's mailbox, then stamps it
+    SplitMail* dst = &pt.mail[lane]->split[pt.seq & 1u][root ? 0 : (k * 2 + c)][pt.rank];
+    dst->s = fb[bi];
+    dst->tot_g = tg; dst->tot_h = th;
+    __threadfence_system();
+    StoreReleaseSys(&dst->seq, pt.seq);
+  }
 }
 
 template <bool QUANT>
-__global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
-                                                 const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
-                                                 BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
-                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
+__global__ void __launch_bounds__(kFindWarps * 32, 2) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
+                                                             const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
+                                                             BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
+                                                             unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
   PdlLaunchDependents();
   LGB_TRACE(ctrl, 30);
   PdlWait();
@@ -513,17 +530,18 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
   if (Finished(ctrl)) return;
   const int k = blockIdx.z;
   if (!root && k >= ctrl->batch_n) return;
-  int f = blockIdx.x;
+  int f = blockIdx.x * kFindWarps + (threadIdx.x >> 5);
   if (pt.world > 0) {      // every rank's histograms of this exchange must be complete: their words arrive in this rank's own mailbox
-    if (pt.sliced) { f += pt.f_lo; if (f >= pt.f_hi) return; }
     __shared__ int s_ok;
     if (threadIdx.x == 0) s_ok = 1;
     __syncthreads();
     if (threadIdx.x < pt.world && !PeerWait(&pt.mail[pt.rank]->hist_flag[threadIdx.x], pt.seq, pt, ctrl)) s_ok = 0;
     __syncthreads();
     if (!s_ok) return;
+    if (pt.sliced) f += pt.f_lo;
   }
-  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, 0, &pt);
+  const int f_end = (pt.world > 0 && pt.sliced) ? pt.f_hi : P.num_features;
+  if (f < f_end) FindUnitWarp<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, pt);
   LGB_TRACE(ctrl, 32);
 }
 

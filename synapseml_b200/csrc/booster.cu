@@ -614,17 +614,17 @@ void Booster::LaunchHist(bool root) {
 }
 
 void Booster::LaunchFind(bool root) {
-  const int fgrid = peers_.sliced ? CeilDiv(F_, peers_.world) : F_;      // sliced: the largest feature range of any rank
-  dim3 grid(fgrid, root ? 1 : 2, root ? 1 : max_batch_);
+  const int funits = peers_.sliced ? CeilDiv(F_, peers_.world) : F_;      // sliced: the largest feature range of any rank
+  dim3 grid(CeilDiv(funits, kFindWarps), root ? 1 : 2, root ? 1 : max_batch_);      // a warp per (feature, child, batch item)
   PeerTable pt = peers_;
   pt.seq = exchange_seq_;
   pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
   long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
   if (lp_.quantized)
-    LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+    LaunchPdl(k_bt_find<true>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
               d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   else
-    LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+    LaunchPdl(k_bt_find<false>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
               d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
   ++launches_;
 }

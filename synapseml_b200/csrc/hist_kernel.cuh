@@ -113,7 +113,7 @@ template <int R, int BPL, bool FLT, bool ROOT, bool PACK = false>
 __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride, const uint16_t* __restrict__ gh16,
                                          const int2* __restrict__ ghfix, const int* idx, int begin, int lo, int hi,
                                          unsigned lane_addr, unsigned int* hsm, long long* work, int F, int tile,
-                                         int rows_per_flush, bool kmask) {
+                                         int rows_per_flush, bool kmask, unsigned long long* t_flush = nullptr) {
   constexpr int LPR = 32 / R;
   constexpr int FT = LPR * BPL;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -234,6 +234,7 @@ __device__ __forceinline__ void HistRows(const uint8_t* rmc, unsigned rm_stride,
       }
     }
     __syncthreads();
+    if (t_flush != nullptr && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(*t_flush));      // timeline experiments
     HistFlush<R, BPL, FLT, PACK>(hsm, work, F, tile);
     __syncthreads();
   }

@@ -406,21 +406,27 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
   return s;
 }
 
-// Split search runs on 256-thread sub-blocks (one per feature x child); a CTA may hold more than one of them (the persistent
-// tree kernel runs four), so they synchronise on named barriers instead of __syncthreads().
+// 256-thread sub-blocks of a CTA synchronise on named barriers instead of __syncthreads() (the partition kernel's tiles, the replay).
 constexpr int kFindThreads = 256;
 constexpr int kMaxFindSubs = 4;
 __device__ __forceinline__ void SubSync(int sub) { asm volatile("bar.sync %0, %1;" ::"r"(sub + 1), "n"(kFindThreads) : "memory"); }
 
 struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right: reverse, left: forward)
 
-// block-wide argmax of candidates; ties on gain go to the larger (reverse scan) or smaller (forward scan) bin, which is
-// what a sequential scan with a strict '>' keeps
-__device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand* s_c /*[8]*/, int sub) {
-  const int lane = threadIdx.x & 31, warp = (threadIdx.x & (kFindThreads - 1)) >> 5;
-  auto better = [&](const Cand& t, const Cand& cur) {
-    return (t.gain > cur.gain) || (t.gain == cur.gain && t.b >= 0 && (cur.b < 0 || (prefer_larger_b ? t.b > cur.b : t.b < cur.b)));
-  };
+// ------------------------------------------------------------------------------------------------ K6 as a warp scan
+// One WARP searches one feature of one leaf: lane l owns bins [8 l, 8 l + 8) — eight 16-byte histogram entries, one coalesced
+// 4 KB read per warp — sums them, the lane totals are prefix-summed with shuffles, and every lane evaluates its eight thresholds
+// (the same expressions, in the same order, as the sequential scan: FindBestThresholdSequentially / ...Int with a reverse
+// scan, plus a forward scan when the feature has a NaN bin and more than two bins).  The arg-max over thresholds keeps the
+// sequential scan's tie rules (reverse: the larger bin on equal gain, forward: the smaller).  No shared memory, no block
+// barrier: 2000 features x 2 children x 8 leaves are 32000 warps (3-4 waves) instead of 32000 256-thread CTAs (27 waves).
+// g_in / h_in: the lane's eight bins of the leaf's histogram.  The result is written by lane 0.
+constexpr int kBinsPerLane = kBins / 32;
+
+__device__ __forceinline__ bool CandBetter(const Cand& t, const Cand& cur, bool prefer_larger_b) {
+  return (t.gain > cur.gain) || (t.gain == cur.gain && t.b >= 0 && (cur.b < 0 || (prefer_larger_b ? t.b > cur.b : t.b < cur.b)));
+}
+__device__ __forceinline__ Cand WarpBestCand(Cand c, bool prefer_larger_b) {
   for (int o = 16; o > 0; o >>= 1) {
     Cand t;
     t.gain = __shfl_xor_sync(0xffffffffu, c.gain, o);
@@ -428,49 +434,28 @@ __device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand
     t.sg = __shfl_xor_sync(0xffffffffu, c.sg, o);
     t.sh = __shfl_xor_sync(0xffffffffu, c.sh, o);
     t.cnt = __shfl_xor_sync(0xffffffffu, c.cnt, o);
-    if (better(t, c)) c = t;
+    if (CandBetter(t, c, prefer_larger_b)) c = t;
   }
-  SubSync(sub);
-  if (lane == 0) s_c[warp] = c;
-  SubSync(sub);
-  Cand r = s_c[0];
-  #pragma unroll
-  for (int w = 1; w < 8; ++w) if (better(s_c[w], r)) r = s_c[w];
-  return r;
+  return c;
 }
 
-// One 256-thread CTA searches one feature of one leaf, one bin per thread.  Implements FindBestThresholdSequentially /
-// ...Int (reverse scan, plus a forward scan when the feature has a NaN bin and more than two bins) with block-wide prefix
-// sums: the sequential `continue` / `break` conditions are monotone in the scan position, so they become per-threshold
-// predicates.  g_in/h_in: this thread's bin of the leaf's histogram.  Result valid in thread 0.
 template <bool QUANT>
-__device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
-                              long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
-                              double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
-                              long long* out_tot_g, long long* out_tot_h, int sub) {
-  __shared__ long long s_g_all[kMaxFindSubs][8], s_h_all[kMaxFindSubs][8];
-  __shared__ int s_c_all[kMaxFindSubs][8];
-  __shared__ Cand s_cand_all[kMaxFindSubs][8];
-  __shared__ int s_flag_all[kMaxFindSubs];
-  long long* s_g = s_g_all[sub]; long long* s_h = s_h_all[sub]; int* s_c = s_c_all[sub]; Cand* s_cand = s_cand_all[sub];
-  int& s_flag = s_flag_all[sub];
-  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
+__device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLane], const long long (&h_in)[kBinsPerLane], const FeatureMetaDev fm,
+                                             int f, bool root, long long tot_g, long long tot_h, double leaf_sum_g, double leaf_sum_h,
+                                             int num_data, const LearnerParams& P, double gscale, double hscale, SplitDev* out,
+                                             unsigned char* splittable_out, long long* out_tot_g, long long* out_tot_h) {
+  const int lane = threadIdx.x & 31;
   const int num_bin = fm.num_bin;
   const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
   const int nan_bin = two_scans ? num_bin - 1 : -1;
-  if (b == 0) s_flag = 0;
-  // pass 0 (root only): leaf totals = sum of all bins of this feature
-  if (root) {
-    long long tg = g_in, th = h_in;
-    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
-    if (lane == 0) { s_g[warp] = tg; s_h[warp] = th; }
-    SubSync(sub);
-    tot_g = 0; tot_h = 0;
+  if (root) {      // the leaf totals = the sum of all bins of this feature
+    long long tg = 0, th = 0;
     #pragma unroll
-    for (int w = 0; w < 8; ++w) { tot_g += s_g[w]; tot_h += s_h[w]; }
+    for (int j = 0; j < kBinsPerLane; ++j) { tg += g_in[j]; th += h_in[j]; }
+    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
+    tot_g = tg; tot_h = th;
     leaf_sum_g = static_cast<double>(tot_g) * gscale;
     leaf_sum_h = static_cast<double>(tot_h) * hscale;
-    SubSync(sub);
   }
   *out_tot_g = tot_g; *out_tot_h = tot_h;
   double sum_gradient, sum_hessian, cnt_factor;
@@ -483,83 +468,104 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     sum_hessian = leaf_sum_h + 2 * KEPS;
     cnt_factor = num_data / sum_hessian;
   }
-  const bool use = b < num_bin && b != nan_bin;
-  const long long gv = use ? g_in : 0, hv = use ? h_in : 0;
-  const int cv = (!QUANT && use) ? RoundIntD(static_cast<double>(hv) * hscale * cnt_factor) : 0;
-  // inclusive block scan
-  long long pg = gv, ph = hv; int pc = cv;
+  // the lane's totals over its (masked) bins; the bins are walked again below with a running prefix, so only the raw bins stay live
+  auto masked = [&](int j, long long* g, long long* h, int* cnt) {
+    const int b = lane * kBinsPerLane + j;
+    const bool use = b < num_bin && b != nan_bin;
+    *g = use ? g_in[j] : 0; *h = use ? h_in[j] : 0;
+    *cnt = (!QUANT && use) ? RoundIntD(static_cast<double>(*h) * hscale * cnt_factor) : 0;
+  };
+  long long lg = 0, lh = 0; int lc = 0;
+  #pragma unroll
+  for (int j = 0; j < kBinsPerLane; ++j) {
+    long long g, h; int cn;
+    masked(j, &g, &h, &cn);
+    lg += g; lh += h; lc += cn;
+  }
+  // exclusive prefix of the lane totals over the warp, and the totals
+  long long og = lg, oh = lh; int oc = lc;
   #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const long long tg = __shfl_up_sync(0xffffffffu, pg, o);
-    const long long th = __shfl_up_sync(0xffffffffu, ph, o);
-    const int tc = __shfl_up_sync(0xffffffffu, pc, o);
-    if (lane >= o) { pg += tg; ph += th; pc += tc; }
+    const long long tg = __shfl_up_sync(0xffffffffu, og, o);
+    const long long th = __shfl_up_sync(0xffffffffu, oh, o);
+    const int tc = __shfl_up_sync(0xffffffffu, oc, o);
+    if (lane >= o) { og += tg; oh += th; oc += tc; }
   }
-  if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
-  SubSync(sub);
-  long long Tg = 0, Th = 0; int Tc = 0;
-  #pragma unroll
-  for (int w = 0; w < 8; ++w) {
-    if (w < warp) { pg += s_g[w]; ph += s_h[w]; pc += s_c[w]; }
-    Tg += s_g[w]; Th += s_h[w]; Tc += s_c[w];
-  }
+  const long long Tg = __shfl_sync(0xffffffffu, og, 31), Th = __shfl_sync(0xffffffffu, oh, 31);
+  const int Tc = __shfl_sync(0xffffffffu, oc, 31);
+  og -= lg; oh -= lh; oc -= lc;      // what the lower lanes hold
   const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
   const double min_gain_shift = gain_shift + P.min_gain_to_split;
   bool splittable = false;
-  // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
   const int top = num_bin - 1 - (two_scans ? 1 : 0);
   Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
-  if (b >= 1 && b <= top) {
-    const long long rgi = Tg - (pg - gv), rhi = Th - (ph - hv);
-    double gain = 0.0; int rc; bool ok = true;
-    if (QUANT) {
-      rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
-      const double srh = static_cast<double>(rhi) * hscale;
-      const int lc = num_data - rc;
-      const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
-      const double slh = static_cast<double>(lhi) * hscale;
-      ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
-      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
-    } else {
-      rc = Tc - (pc - cv);
-      const double rh = KEPS + static_cast<double>(rhi) * hscale;
-      const int lc = num_data - rc;
-      const double lh = sum_hessian - rh;
-      ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
-      if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
+  Cand cf = cr;
+  #pragma unroll
+  for (int j = 0; j < kBinsPerLane; ++j) {
+    const int b = lane * kBinsPerLane + j;
+    long long gvj, hvj; int cvj;
+    masked(j, &gvj, &hvj, &cvj);
+    og += gvj; oh += hvj; oc += cvj;
+    const long long ipg = og, iph = oh;      // inclusive prefix over bins [0, b]
+    const int ipc = oc;
+    // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
+    if (b >= 1 && b <= top) {
+      const long long rgi = Tg - (ipg - gvj), rhi = Th - (iph - hvj);
+      double gain = 0.0; int rc; bool ok = true;
+      if (QUANT) {
+        rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+        const double srh = static_cast<double>(rhi) * hscale;
+        const int lcn = num_data - rc;
+        const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
+        const double slh = static_cast<double>(lhi) * hscale;
+        ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lcn < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
+        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      } else {
+        rc = Tc - (ipc - cvj);
+        const double rh = KEPS + static_cast<double>(rhi) * hscale;
+        const int lcn = num_data - rc;
+        const double lhh = sum_hessian - rh;
+        ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lcn < P.min_data_in_leaf) && !(lhh < P.min_sum_hessian);
+        if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lhh, rg, rh, P); }
+      }
+      if (ok && gain > min_gain_shift) {
+        splittable = true;
+        Cand t; t.gain = gain; t.b = b; t.sg = rgi; t.sh = rhi; t.cnt = rc;
+        if (CandBetter(t, cr, true)) cr = t;
+      }
     }
-    if (ok && gain > min_gain_shift) { splittable = true; cr.gain = gain; cr.b = b; cr.sg = rgi; cr.sh = rhi; cr.cnt = rc; }
-  }
-  // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
-  Cand cf; cf.gain = KMINSCORE; cf.b = -1; cf.sg = 0; cf.sh = 0; cf.cnt = 0;
-  if (two_scans && b <= num_bin - 2) {
-    const long long lgi = pg, lhi = ph;
-    double gain = 0.0; int lc; bool ok = true;
-    if (QUANT) {
-      lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
-      const double slh = static_cast<double>(lhi) * hscale;
-      const int rc = num_data - lc;
-      const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
-      const double srh = static_cast<double>(rhi) * hscale;
-      ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
-      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
-    } else {
-      lc = pc;
-      const double lh = KEPS + static_cast<double>(lhi) * hscale;
-      const int rc = num_data - lc;
-      const double rh = sum_hessian - lh;
-      ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
-      if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
+    // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
+    if (two_scans && b <= num_bin - 2) {
+      const long long lgi = ipg, lhi = iph;
+      double gain = 0.0; int lcn; bool ok = true;
+      if (QUANT) {
+        lcn = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        const double slh = static_cast<double>(lhi) * hscale;
+        const int rc = num_data - lcn;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double srh = static_cast<double>(rhi) * hscale;
+        ok = !(lcn < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
+        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      } else {
+        lcn = ipc;
+        const double lhh = KEPS + static_cast<double>(lhi) * hscale;
+        const int rc = num_data - lcn;
+        const double rh = sum_hessian - lhh;
+        ok = !(lcn < P.min_data_in_leaf || lhh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
+        if (ok) { const double lgd = static_cast<double>(lgi) * gscale; gain = SplitGainD(lgd, lhh, sum_gradient - lgd, rh, P); }
+      }
+      if (ok && gain > min_gain_shift) {
+        splittable = true;
+        Cand t; t.gain = gain; t.b = b; t.sg = lgi; t.sh = lhi; t.cnt = lcn;
+        if (CandBetter(t, cf, false)) cf = t;
+      }
     }
-    if (ok && gain > min_gain_shift) { splittable = true; cf.gain = gain; cf.b = b; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }
   }
-  if (splittable) s_flag = 1;
-  const Cand best_r = BlockBestCand(cr, true, s_cand, sub);
+  const bool any = __any_sync(0xffffffffu, splittable);
+  const Cand best_r = WarpBestCand(cr, true);
   Cand best_f = cf;
-  if (two_scans) best_f = BlockBestCand(cf, false, s_cand, sub);
-  SubSync(sub);
-  if (b == 0) {
-    const bool any = s_flag != 0;
+  if (two_scans) best_f = WarpBestCand(cf, false);
+  if (lane == 0) {
     SplitDev s = EmptySplit(f, fm.real_index);
     s.missing_type = fm.missing_type;
     s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;

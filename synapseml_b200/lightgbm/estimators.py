@@ -177,6 +177,23 @@ class LightGBMBase:
         keep = rng.random(len(hd)) < fraction
         return hd[keep]
 
+    def _sample_across_ranks(self, df, total_rows, counts, rank, dist):
+        """The reference samples the WHOLE DataFrame on the driver (df.limit / df.sample run over all partitions).  With one process
+        per GPU the rows of the other ranks are not in this process: in "fixed" mode (the first numSamples rows of the global order)
+        every rank hands the part of its rows that falls inside that head to rank 0; the other modes sample rank 0's rows only."""
+        if dist is None or self._p["samplingMode"] != "fixed":
+            return self.get_sampled_rows(df, total_rows) if rank == 0 else None
+        num_samples = min(self.getBinSampleCount(), total_rows)
+        before = int(sum(counts[:rank]))
+        k = int(min(max(num_samples - before, 0), counts[rank]))
+        mine = self.get_sampled_rows(df, k) if k > 0 else None      # "fixed": the first k local rows
+        parts = [None] * dist.get_world_size() if rank == 0 else None
+        dist.gather_object(mine, parts, dst=0)
+        if rank != 0:
+            return None
+        parts = [p for p in parts if p is not None]
+        return parts[0] if len(parts) == 1 else np.concatenate(parts)
+
     def preprocess_data(self, df):
         return df
 
@@ -224,8 +241,8 @@ class LightGBMBase:
             if serialized is None:
                 t0 = time.time()
                 payload = [None]
+                sampled = self._sample_across_ranks(df, total_rows, counts if dist_on else None, rank, dist if dist_on else None)
                 if rank == 0:     # the driver samples and finds the bin boundaries (K1), everyone else receives the bytes
-                    sampled = self.get_sampled_rows(df, total_rows)
                     payload[0] = ReferenceDatasetUtils.create_reference_dataset_from_sample(ds_params, g["featuresCol"], total_rows,
                                                                                             num_cols, sampled)
                 if dist_on:

@@ -83,6 +83,17 @@ nm.free_lightgbm_network()
 counts = [None, None]
 dist.all_gather_object(counts, 1000 + dist.get_rank())
 assert counts == [1000, 1001]
+# the bin sample is taken from the head of the GLOBAL row order (df.limit in the reference), whichever ranks hold those rows
+import numpy as np
+from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LocalDataFrame
+rk = dist.get_rank()
+Xl = np.arange(rk * 30 * 3, (rk + 1) * 30 * 3, dtype=np.float64).reshape(30, 3)
+est = LightGBMClassifier(samplingMode="fixed", binSampleCount=40)
+got = est._sample_across_ranks(LocalDataFrame.from_arrays(Xl, np.zeros(30, dtype=np.float32), num_partitions=2), 60, [30, 30], rk, dist)
+if rk == 0:
+    assert got.shape == (40, 3) and np.array_equal(got, np.arange(120, dtype=np.float64).reshape(40, 3)), got
+else:
+    assert got is None
 dist.barrier()
 open(os.path.join(%(out)r, "rank%%d.ok" %% dist.get_rank()), "w").write("ok")
 """
