@@ -519,7 +519,7 @@ __device__ __forceinline__ void FindUnitWarp(const long long* work, int work_ele
 }
 
 template <bool QUANT>
-__global__ void __launch_bounds__(kFindWarps * 32, 2) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
+__global__ void __launch_bounds__(kFindWarps * 32, 2) k_bt_find_warp(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
                                                              const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
                                                              BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
                                                              unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
@@ -542,6 +542,204 @@ __global__ void __launch_bounds__(kFindWarps * 32, 2) k_bt_find(const long long*
   }
   const int f_end = (pt.world > 0 && pt.sliced) ? pt.f_hi : P.num_features;
   if (f < f_end) FindUnitWarp<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, pt);
+  LGB_TRACE(ctrl, 32);
+}
+
+// ---- the same search with a 256-thread CTA per unit (one bin per thread, block-wide scans): one threshold per thread makes a
+// unit's latency half that of the warp form (4.4 vs 9.4 us, B200), so it is what narrow data uses, where a round has only a few
+// hundred units (C2: 28 x 2 x 8) and is bound by latency; the warp form wins when the units no longer fit one wave (C5: 32000).
+template <bool QUANT>
+__device__ __forceinline__ void FindUnit(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
+                                         NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
+                                         const LearnerParams& P, int root, int f, int c, int k, int sub, const PeerTable* pt = nullptr) {
+  __shared__ int s_last_all[kMaxFindSubs];
+  __shared__ double s_gain_all[kMaxFindSubs][8];
+  __shared__ int s_feat_all[kMaxFindSubs][8], s_idx_all[kMaxFindSubs][8];
+  int& s_last = s_last_all[sub];
+  double* s_gain = s_gain_all[sub]; int* s_feat = s_feat_all[sub]; int* s_idx = s_idx_all[sub];
+  const int F = P.num_features;
+  const int b = threadIdx.x & (kFindThreads - 1);
+  // feature-sliced exchange: this rank owns features [f_first, f_first + nf) and sends the best of them to every rank
+  const bool sliced = pt != nullptr && pt->world > 0 && pt->sliced != 0;
+  const int f_first = sliced ? pt->f_lo : 0;
+  const int nf = sliced ? pt->f_hi - pt->f_lo : F;
+  // ---- which node is this, and what do we know about it
+  NodeDev me;              // what gets published for the child (root: only the fields the search needs)
+  int node, parent = -1, parent_slot = 0, side = 0;
+  bool find = true;
+  if (root) {
+    node = 0;
+    me = nodes[0];
+  } else {
+    const BatchItem& it = ctrl->batch[k];
+    const ChildGeom g = MakeGeom(it, ctrl->part_cursor[k], P);
+    const bool is_left = (c == 0) == g.left_smaller;      // c == 0: the smaller child (its histogram was just built)
+    node = is_left ? it.left : it.right;
+    side = is_left ? 0 : 1;
+    parent = it.node;
+    parent_slot = it.parent_slot;
+    find = g.find;
+    me.begin = is_left ? it.src_begin : g.rbegin;
+    me.count = is_left ? g.nl : g.nr;
+    me.buf = g.buf;
+    me.global_count = is_left ? g.lc : g.rc;
+    me.int_g = is_left ? it.left_int_g : it.right_int_g; me.int_h = is_left ? it.left_int_h : it.right_int_h;
+    me.sum_g = is_left ? it.left_sum_g : it.right_sum_g; me.sum_h = is_left ? it.left_sum_h : it.right_sum_h;
+    me.depth = it.child_depth;
+    me.hist_slot = c == 0 ? it.fresh_slot : it.parent_slot;     // the larger child takes over the parent's slot
+    me.state = 0; me.left = me.right = -1; me.pad_ = 0;
+  }
+  me.child_feat[0] = me.child_feat[1] = -1; me.child_count[0] = me.child_count[1] = 0; me.child_gain[0] = me.child_gain[1] = KMINSCORE;
+  if (!find) {         // children that are not searched are published by their first unit alone
+    if (f != f_first) return;
+    if (b == 0) {
+      me.best = EmptySplit(-1, -1);
+      nodes[node] = me;
+      nodes[parent].child_gain[side] = KMINSCORE; nodes[parent].child_feat[side] = -1; nodes[parent].child_count[side] = me.global_count;
+      __threadfence();
+    }
+    return;
+  }
+  const FeatureMetaDev fm = fmeta[f];
+  const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
+  const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
+  const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
+  longlong2 v;
+  const size_t item_off = static_cast<size_t>(root ? 0 : k) * work_elems;
+  if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
+    long long a = 0, bsum = 0;
+    for (int r = 0; r < pt->world; ++r) {
+      const long long* w = pt->work[r] + pt->parity_off + item_off;
+      if (QUANT) a += w[static_cast<size_t>(f) * kBins + b];
+      else { const longlong2 t = *reinterpret_cast<const longlong2*>(w + off); a += t.x; bsum += t.y; }
+    }
+    if (QUANT) { v.y = a & 0xffffffffLL; v.x = (a - v.y) >> 32; }
+    else { v.x = a; v.y = bsum; }
+  } else if (QUANT) {     // packed work area: (sum g << 32) + sum h
+    const long long pk = work[item_off + static_cast<size_t>(f) * kBins + b];
+    v.y = pk & 0xffffffffLL;
+    v.x = (pk - v.y) >> 32;
+  } else {
+    v = *reinterpret_cast<const longlong2*>(work + item_off + off);
+  }
+  bool used = true;
+  if (!root) {
+    used = splittable[static_cast<size_t>(parent) * F + f] != 0;
+    if (c == 1) {
+      const longlong2 p = *reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(parent_slot) * slot_stride + off);
+      v.x = p.x - v.x; v.y = p.y - v.y;
+    }
+  }
+  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
+  SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
+  unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
+  long long tg = me.int_g, th = me.int_h;
+  // column sample of this tree (feature_fraction): a feature outside it has no split.  At the root it still runs the search,
+  // because the leaf totals come out of it, and its result is discarded.
+  const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
+  if (!used || (!sampled && !root)) {
+    if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
+  } else {
+    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                         fb + f, spl, &tg, &th, sub);
+    if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
+  }
+  if (P.reduce_in_select && !sliced) {
+    // the replay kernel picks the child's best feature (SelectReduceChildren); the first unit publishes everything else
+    if (f == 0 && b == 0) {
+      if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
+        me.int_g = tg; me.int_h = th;
+        me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
+      }
+      NodeDev& N = nodes[node];
+      N.begin = me.begin; N.count = me.count; N.buf = me.buf; N.global_count = me.global_count;
+      N.int_g = me.int_g; N.int_h = me.int_h; N.sum_g = me.sum_g; N.sum_h = me.sum_h;
+      N.depth = me.depth; N.hist_slot = me.hist_slot; N.state = me.state; N.left = me.left; N.right = me.right; N.pad_ = 0;
+      N.child_feat[0] = N.child_feat[1] = -1; N.child_count[0] = N.child_count[1] = 0;
+      N.child_gain[0] = N.child_gain[1] = KMINSCORE;
+    }
+    SubSync(sub);
+    return;
+  }
+  __threadfence();
+  SubSync(sub);
+  if (b == 0) s_last = (atomicAdd(&ctrl->find_count[root ? 0 : k][c], 1) == nf - 1);
+  SubSync(sub);
+  if (s_last) {       // the last unit of this child reduces over the (rank's) features and publishes the child
+    __threadfence();
+    double bg = KMINSCORE; int bf = -1, bi = -1;
+    for (int j = f_first + b; j < f_first + nf; j += kFindThreads) {
+      const double g = fb[j].gain; const int rf = fb[j].real_feature;
+      if (bi < 0 || SplitBetter(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+    }
+    const int lane = b & 31, warp = b >> 5;
+    for (int o = 16; o > 0; o >>= 1) {
+      const double g = __shfl_xor_sync(0xffffffffu, bg, o);
+      const int rf = __shfl_xor_sync(0xffffffffu, bf, o);
+      const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (i >= 0 && (bi < 0 || SplitBetter(g, rf, bg, bf))) { bg = g; bf = rf; bi = i; }
+    }
+    if (lane == 0) { s_gain[warp] = bg; s_feat[warp] = bf; s_idx[warp] = bi; }
+    SubSync(sub);
+    if (b == 0) {
+      bg = s_gain[0]; bf = s_feat[0]; bi = s_idx[0];
+      for (int w = 1; w < 8; ++w)
+        if (s_idx[w] >= 0 && (bi < 0 || SplitBetter(s_gain[w], s_feat[w], bg, bf))) { bg = s_gain[w]; bf = s_feat[w]; bi = s_idx[w]; }
+      if (root) {        // the root's totals come out of the search itself (every feature sees the same sums)
+        me.int_g = tg; me.int_h = th;
+        me.sum_g = static_cast<double>(tg) * gscale; me.sum_h = static_cast<double>(th) * hscale;
+      }
+      if (sliced) {      // the child's best split is chosen by the replay kernel from all ranks' records (SelectReducePeers)
+        me.best = EmptySplit(-1, -1);
+        nodes[node] = me;
+        s_idx[0] = bi;
+      } else {
+        me.best = fb[bi];
+        nodes[node] = me;
+        if (!root) {
+          nodes[parent].child_gain[side] = me.best.gain; nodes[parent].child_feat[side] = me.best.real_feature;
+          nodes[parent].child_count[side] = me.global_count;
+        }
+      }
+      ctrl->find_count[root ? 0 : k][c] = 0;
+    }
+    if (sliced) {        // thread r stores this rank's record into rank r's mailbox, then stamps it
+      SubSync(sub);
+      if (b < pt->world) {
+        SplitMail* dst = &pt->mail[b]->split[pt->seq & 1u][root ? 0 : (k * 2 + c)][pt->rank];
+        dst->s = fb[s_idx[0]];
+        dst->tot_g = tg; dst->tot_h = th;
+        __threadfence_system();
+        StoreReleaseSys(&dst->seq, pt->seq);
+      }
+    }
+  }
+  SubSync(sub);       // the sub-block's shared scratch is reused by its next unit
+}
+
+template <bool QUANT>
+__global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
+                                                 const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
+                                                 BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
+                                                 unsigned char* __restrict__ splittable, LearnerParams P, int root, PeerTable pt) {
+  PdlLaunchDependents();
+  LGB_TRACE(ctrl, 30);
+  PdlWait();
+  LGB_TRACE(ctrl, 31);
+  if (Finished(ctrl)) return;
+  const int k = blockIdx.z;
+  if (!root && k >= ctrl->batch_n) return;
+  int f = blockIdx.x;
+  if (pt.world > 0) {      // every rank's histograms of this exchange must be complete: their words arrive in this rank's own mailbox
+    if (pt.sliced) { f += pt.f_lo; if (f >= pt.f_hi) return; }
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) s_ok = 1;
+    __syncthreads();
+    if (threadIdx.x < pt.world && !PeerWait(&pt.mail[pt.rank]->hist_flag[threadIdx.x], pt.seq, pt, ctrl)) s_ok = 0;
+    __syncthreads();
+    if (!s_ok) return;
+  }
+  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, 0, &pt);
   LGB_TRACE(ctrl, 32);
 }
 

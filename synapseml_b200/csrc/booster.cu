@@ -118,6 +118,9 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
   // search's last unit does, as for wide data)
   lp_.reduce_in_select = F_ <= 32 && !(getenv("LGB_B200_REDUCE_IN_SELECT") && atoi(getenv("LGB_B200_REDUCE_IN_SELECT")) == 0);
+  // split search: a CTA per unit while a round's units fit about one wave of CTAs (8 per SM), a warp per unit beyond that
+  find_warp_ = static_cast<long long>(F_) * 2 * kMaxBatch > 148LL * 8 * 2;
+  if (const char* env = getenv("LGB_B200_FIND_WARP")) find_warp_ = atoi(env) != 0;
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -571,9 +574,8 @@ void Booster::LaunchHist(bool root) {
     const int per_copy = std::min(32767 / (qb / 2 + 1), 65535 / (qb + 1));
     rows_per_flush = std::max(32, (per_copy * R) / 32 * 32);
   }
-  // non-root launches find their work areas already cleared by k_bt_part_scatter
-  // the work areas alternate between two buffers from one histogram launch to the next (peer exchange: batch_tree.cuh; fused
-  // expansion: the split search clears the buffer of the next launch)
+  // non-root launches find their work areas already cleared by the partition kernel; the work areas alternate between two
+  // buffers from one histogram launch to the next (what the peer exchange needs: batch_tree.cuh)
   PeerTable pt = peers_;
   ++exchange_seq_;
   pt.seq = exchange_seq_;
@@ -615,17 +617,28 @@ void Booster::LaunchHist(bool root) {
 
 void Booster::LaunchFind(bool root) {
   const int funits = peers_.sliced ? CeilDiv(F_, peers_.world) : F_;      // sliced: the largest feature range of any rank
-  dim3 grid(CeilDiv(funits, kFindWarps), root ? 1 : 2, root ? 1 : max_batch_);      // a warp per (feature, child, batch item)
   PeerTable pt = peers_;
   pt.seq = exchange_seq_;
   pt.parity_off = (exchange_seq_ & 1u) * work_stride_;
   long long* work = d_hist_work_.p + (exchange_seq_ & 1u) * work_stride_;
-  if (lp_.quantized)
-    LaunchPdl(k_bt_find<true>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
-  else
-    LaunchPdl(k_bt_find<false>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-              d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+  // narrow data: a 256-thread CTA per (feature, child, batch item) — a few hundred CTAs, lowest latency; wide data: a warp per unit
+  if (!find_warp_) {
+    dim3 grid(funits, root ? 1 : 2, root ? 1 : max_batch_);
+    if (lp_.quantized)
+      LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+    else
+      LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+  } else {
+    dim3 grid(CeilDiv(funits, kFindWarps), root ? 1 : 2, root ? 1 : max_batch_);
+    if (lp_.quantized)
+      LaunchPdl(k_bt_find_warp<true>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+    else
+      LaunchPdl(k_bt_find_warp<false>, grid, dim3(kFindWarps * 32), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
+                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+  }
   ++launches_;
 }
 

@@ -316,6 +316,7 @@ class Booster {
   void PrepareGradients(bool absmax_ready);           // absmax -> scales -> quantize / fixed point
   void TrainTree(HostTree* out);
   void LaunchHist(bool root);
+  bool find_warp_ = false;      // split search: a warp (wide data) or a 256-thread CTA (narrow data) per (feature, child, batch item)
   void LaunchFind(bool root);
   void EnqueueRounds(int rounds);
   void LaunchSelect(bool after_root);

@@ -413,6 +413,197 @@ __device__ __forceinline__ void SubSync(int sub) { asm volatile("bar.sync %0, %1
 
 struct Cand { double gain; int b; long long sg, sh; int cnt; };   // sums of the scanned side (right: reverse, left: forward)
 
+// block-wide argmax of candidates; ties on gain go to the larger (reverse scan) or smaller (forward scan) bin, which is
+// what a sequential scan with a strict '>' keeps
+__device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand* s_c /*[8]*/, int sub) {
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x & (kFindThreads - 1)) >> 5;
+  auto better = [&](const Cand& t, const Cand& cur) {
+    return (t.gain > cur.gain) || (t.gain == cur.gain && t.b >= 0 && (cur.b < 0 || (prefer_larger_b ? t.b > cur.b : t.b < cur.b)));
+  };
+  for (int o = 16; o > 0; o >>= 1) {
+    Cand t;
+    t.gain = __shfl_xor_sync(0xffffffffu, c.gain, o);
+    t.b = __shfl_xor_sync(0xffffffffu, c.b, o);
+    t.sg = __shfl_xor_sync(0xffffffffu, c.sg, o);
+    t.sh = __shfl_xor_sync(0xffffffffu, c.sh, o);
+    t.cnt = __shfl_xor_sync(0xffffffffu, c.cnt, o);
+    if (better(t, c)) c = t;
+  }
+  SubSync(sub);
+  if (lane == 0) s_c[warp] = c;
+  SubSync(sub);
+  Cand r = s_c[0];
+  #pragma unroll
+  for (int w = 1; w < 8; ++w) if (better(s_c[w], r)) r = s_c[w];
+  return r;
+}
+
+// One 256-thread CTA searches one feature of one leaf, one bin per thread.  Implements FindBestThresholdSequentially /
+// ...Int (reverse scan, plus a forward scan when the feature has a NaN bin and more than two bins) with block-wide prefix
+// sums: the sequential `continue` / `break` conditions are monotone in the scan position, so they become per-threshold
+// predicates.  g_in/h_in: this thread's bin of the leaf's histogram.  Result valid in thread 0.
+template <bool QUANT>
+__device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
+                              long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
+                              double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
+                              long long* out_tot_g, long long* out_tot_h, int sub) {
+  __shared__ long long s_g_all[kMaxFindSubs][8], s_h_all[kMaxFindSubs][8];
+  __shared__ int s_c_all[kMaxFindSubs][8];
+  __shared__ Cand s_cand_all[kMaxFindSubs][8];
+  __shared__ int s_flag_all[kMaxFindSubs];
+  long long* s_g = s_g_all[sub]; long long* s_h = s_h_all[sub]; int* s_c = s_c_all[sub]; Cand* s_cand = s_cand_all[sub];
+  int& s_flag = s_flag_all[sub];
+  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
+  const int num_bin = fm.num_bin;
+  const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
+  const int nan_bin = two_scans ? num_bin - 1 : -1;
+  if (b == 0) s_flag = 0;
+  // pass 0 (root only): leaf totals = sum of all bins of this feature
+  if (root) {
+    long long tg = g_in, th = h_in;
+    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
+    if (lane == 0) { s_g[warp] = tg; s_h[warp] = th; }
+    SubSync(sub);
+    tot_g = 0; tot_h = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) { tot_g += s_g[w]; tot_h += s_h[w]; }
+    leaf_sum_g = static_cast<double>(tot_g) * gscale;
+    leaf_sum_h = static_cast<double>(tot_h) * hscale;
+    SubSync(sub);
+  }
+  *out_tot_g = tot_g; *out_tot_h = tot_h;
+  double sum_gradient, sum_hessian, cnt_factor;
+  if (QUANT) {
+    sum_gradient = static_cast<double>(tot_g) * gscale;
+    sum_hessian = static_cast<double>(tot_h) * hscale;
+    cnt_factor = static_cast<double>(num_data) / static_cast<double>(tot_h);
+  } else {
+    sum_gradient = leaf_sum_g;
+    sum_hessian = leaf_sum_h + 2 * KEPS;
+    cnt_factor = num_data / sum_hessian;
+  }
+  const bool use = b < num_bin && b != nan_bin;
+  const long long gv = use ? g_in : 0, hv = use ? h_in : 0;
+  const int cv = (!QUANT && use) ? RoundIntD(static_cast<double>(hv) * hscale * cnt_factor) : 0;
+  // inclusive block scan
+  long long pg = gv, ph = hv; int pc = cv;
+  #pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long tg = __shfl_up_sync(0xffffffffu, pg, o);
+    const long long th = __shfl_up_sync(0xffffffffu, ph, o);
+    const int tc = __shfl_up_sync(0xffffffffu, pc, o);
+    if (lane >= o) { pg += tg; ph += th; pc += tc; }
+  }
+  if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
+  SubSync(sub);
+  long long Tg = 0, Th = 0; int Tc = 0;
+  #pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    if (w < warp) { pg += s_g[w]; ph += s_h[w]; pc += s_c[w]; }
+    Tg += s_g[w]; Th += s_h[w]; Tc += s_c[w];
+  }
+  const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
+  const double min_gain_shift = gain_shift + P.min_gain_to_split;
+  bool splittable = false;
+  // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
+  const int top = num_bin - 1 - (two_scans ? 1 : 0);
+  Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
+  if (b >= 1 && b <= top) {
+    const long long rgi = Tg - (pg - gv), rhi = Th - (ph - hv);
+    double gain = 0.0; int rc; bool ok = true;
+    if (QUANT) {
+      rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+      const double srh = static_cast<double>(rhi) * hscale;
+      const int lc = num_data - rc;
+      const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
+      const double slh = static_cast<double>(lhi) * hscale;
+      ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
+      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+    } else {
+      rc = Tc - (pc - cv);
+      const double rh = KEPS + static_cast<double>(rhi) * hscale;
+      const int lc = num_data - rc;
+      const double lh = sum_hessian - rh;
+      ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
+      if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
+    }
+    if (ok && gain > min_gain_shift) { splittable = true; cr.gain = gain; cr.b = b; cr.sg = rgi; cr.sh = rhi; cr.cnt = rc; }
+  }
+  // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
+  Cand cf; cf.gain = KMINSCORE; cf.b = -1; cf.sg = 0; cf.sh = 0; cf.cnt = 0;
+  if (two_scans && b <= num_bin - 2) {
+    const long long lgi = pg, lhi = ph;
+    double gain = 0.0; int lc; bool ok = true;
+    if (QUANT) {
+      lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+      const double slh = static_cast<double>(lhi) * hscale;
+      const int rc = num_data - lc;
+      const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+      const double srh = static_cast<double>(rhi) * hscale;
+      ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
+      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+    } else {
+      lc = pc;
+      const double lh = KEPS + static_cast<double>(lhi) * hscale;
+      const int rc = num_data - lc;
+      const double rh = sum_hessian - lh;
+      ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
+      if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
+    }
+    if (ok && gain > min_gain_shift) { splittable = true; cf.gain = gain; cf.b = b; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }
+  }
+  if (splittable) s_flag = 1;
+  const Cand best_r = BlockBestCand(cr, true, s_cand, sub);
+  Cand best_f = cf;
+  if (two_scans) best_f = BlockBestCand(cf, false, s_cand, sub);
+  SubSync(sub);
+  if (b == 0) {
+    const bool any = s_flag != 0;
+    SplitDev s = EmptySplit(f, fm.real_index);
+    s.missing_type = fm.missing_type;
+    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
+    for (int pass = 0; pass < 2; ++pass) {
+      const Cand& c = pass == 0 ? best_r : best_f;
+      if (pass == 1 && !two_scans) break;
+      if (!(any && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      const bool reverse = pass == 0;
+      if (QUANT) {
+        const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double blg = static_cast<double>(lgi) * gscale, blh = static_cast<double>(lhi) * hscale;
+        const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
+        s.threshold = reverse ? c.b - 1 : c.b;
+        s.left_output = LeafOutputD(blg, blh, P);
+        s.left_count = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = lgi; s.left_int_h = lhi;
+        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_count = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+        s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
+      } else {
+        double best_lg, best_lh; int left_count;
+        if (reverse) {
+          const double rg = static_cast<double>(c.sg) * gscale, rh = KEPS + static_cast<double>(c.sh) * hscale;
+          best_lg = sum_gradient - rg; best_lh = sum_hessian - rh; left_count = num_data - c.cnt;
+        } else {
+          best_lg = static_cast<double>(c.sg) * gscale; best_lh = KEPS + static_cast<double>(c.sh) * hscale; left_count = c.cnt;
+        }
+        s.threshold = reverse ? c.b - 1 : c.b;
+        s.left_output = LeafOutputD(best_lg, best_lh, P);
+        s.left_count = left_count;
+        s.left_sum_g = best_lg; s.left_sum_h = best_lh - KEPS;
+        s.right_output = LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P);
+        s.right_count = num_data - left_count;
+        s.right_sum_g = sum_gradient - best_lg; s.right_sum_h = sum_hessian - best_lh - KEPS;
+      }
+      s.gain = c.gain - min_gain_shift;
+      s.default_left = reverse ? 1 : 0;
+    }
+    if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    *out = s;
+    *splittable_out = any ? 1 : 0;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ K6 as a warp scan
 // One WARP searches one feature of one leaf: lane l owns bins [8 l, 8 l + 8) — eight 16-byte histogram entries, one coalesced
 // 4 KB read per warp — sums them, the lane totals are prefix-summed with shuffles, and every lane evaluates its eight thresholds

@@ -200,3 +200,27 @@ def test_full_size_properties(native):
     assert np.allclose(m.predict_raw(X[sub]), nb.scores()[sub], rtol=0, atol=1e-12)   # score update == tree traversal
     nb.free()
     nd.free()
+
+
+@pytest.mark.parametrize("mode", ["quantized", "float"])
+def test_both_split_search_forms_give_the_same_model(native, monkeypatch, mode):
+    """The split search runs as a 256-thread CTA per (feature, child, leaf) on narrow data and as a warp per unit on wide data
+    (LGB_B200_FIND_WARP forces either): same thresholds, gains and tie-breaks, so the same model, on narrow and on wide data."""
+    params = "objective=binary num_leaves=31 max_bin=255 min_data_in_leaf=20 verbosity=-1"
+    if mode == "quantized":
+        params += " use_quantized_grad=true stochastic_rounding=false"
+    Xn, yn = S.higgs_shape(60000)
+    Xw, yw = S.epsilon_shape(6000, f=300)
+    Xw[::7, 3] = np.nan                      # a NaN bin: the forward scan runs too
+    for X, y in ((Xn, yn), (Xw, yw)):
+        models = []
+        for flag in ("0", "1"):
+            monkeypatch.setenv("LGB_B200_FIND_WARP", flag)
+            nd = NativeDataset(X, y, params, micro_batches=[8192])
+            nb = NativeBooster(nd, params)
+            for _ in range(6):
+                nb.update()
+            models.append(strip_parameters(nb.model()))
+            nb.free()
+            nd.free()
+        assert models[0] == models[1]
