@@ -82,7 +82,11 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
   const int num_bin = m.num_bin;
   const double cnt_factor = num_data / sum_hessian;
   bool splittable = false;
-  auto scan = [&](bool reverse, bool na_as_missing) {
+  // skip_default (missing type Zero: FindBestThresholdSequentially<REVERSE, SKIP_DEFAULT_BIN = true, NA_AS_MISSING = false>): the
+  // default bin is neither accumulated nor a threshold, so its rows stay on the side the scan does not build.  The forward scan
+  // starts at histogram entry 0, which is bin 1 when the most frequent bin is bin 0 (upstream leaves that bin out of the histogram
+  // and only the NaN scan reconstructs it).
+  auto scan = [&](bool reverse, bool na_as_missing, bool skip_default = false) {
     double best_lg = std::numeric_limits<double>::quiet_NaN(), best_lh = best_lg;
     double best_gain = kMinScore;
     data_size_t best_left_count = 0;
@@ -91,6 +95,7 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
       double rg = 0.0, rh = kEpsilon;
       data_size_t rc = 0;
       for (int b = num_bin - 1 - (na_as_missing ? 1 : 0); b >= 1; --b) {
+        if (skip_default && b == static_cast<int>(m.default_bin)) continue;
         double g = hist[2 * b], h = hist[2 * b + 1];
         rg += g; rh += h; rc += RoundInt(h * cnt_factor);
         if (rc < p.min_data_in_leaf || rh < p.min_sum_hessian) continue;
@@ -111,7 +116,8 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
     } else {
       double lg = 0.0, lh = kEpsilon;
       data_size_t lc = 0;
-      for (int b = 0; b <= num_bin - 2; ++b) {
+      for (int b = (skip_default && m.most_freq_bin == 0) ? 1 : 0; b <= num_bin - 2; ++b) {
+        if (skip_default && b == static_cast<int>(m.default_bin)) continue;
         double g = hist[2 * b], h = hist[2 * b + 1];
         lg += g; lh += h; lc += RoundInt(h * cnt_factor);
         if (lc < p.min_data_in_leaf || lh < p.min_sum_hessian) continue;
@@ -144,7 +150,10 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
       out->default_left = reverse;
     }
   };
-  if (num_bin > 2 && m.missing_type == MISSING_NAN) {
+  if (num_bin > 2 && m.missing_type == MISSING_ZERO) {
+    scan(true, false, true);
+    scan(false, false, true);
+  } else if (num_bin > 2 && m.missing_type == MISSING_NAN) {
     scan(true, true);
     scan(false, true);
   } else {
@@ -169,13 +178,14 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
   if (int_sum_h <= 0) return false;   // guard (upstream would divide by zero)
   const double cnt_factor = static_cast<double>(num_data) / static_cast<double>(int_sum_h);
   bool splittable = false;
-  auto scan = [&](bool reverse, bool na_as_missing) {
+  auto scan = [&](bool reverse, bool na_as_missing, bool skip_default = false) {
     int64_t best_lg = 0, best_lh = 0;
     double best_gain = kMinScore;
     uint32_t best_threshold = static_cast<uint32_t>(num_bin);
     if (reverse) {
       int64_t rg = 0, rh = 0;
       for (int b = num_bin - 1 - (na_as_missing ? 1 : 0); b >= 1; --b) {
+        if (skip_default && b == static_cast<int>(m.default_bin)) continue;
         rg += hist[2 * b]; rh += hist[2 * b + 1];
         data_size_t rc = RoundInt(static_cast<double>(rh) * cnt_factor);
         double srh = static_cast<double>(rh) * hess_scale;
@@ -193,7 +203,8 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
       }
     } else {
       int64_t lg = 0, lh = 0;
-      for (int b = 0; b <= num_bin - 2; ++b) {
+      for (int b = (skip_default && m.most_freq_bin == 0) ? 1 : 0; b <= num_bin - 2; ++b) {
+        if (skip_default && b == static_cast<int>(m.default_bin)) continue;
         lg += hist[2 * b]; lh += hist[2 * b + 1];
         data_size_t lc = RoundInt(static_cast<double>(lh) * cnt_factor);
         double slh = static_cast<double>(lh) * hess_scale;
@@ -227,7 +238,10 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
       out->default_left = reverse;
     }
   };
-  if (num_bin > 2 && m.missing_type == MISSING_NAN) {
+  if (num_bin > 2 && m.missing_type == MISSING_ZERO) {
+    scan(true, false, true);
+    scan(false, false, true);
+  } else if (num_bin > 2 && m.missing_type == MISSING_NAN) {
     scan(true, true);
     scan(false, true);
   } else {
@@ -332,7 +346,6 @@ class Booster {
     else throw std::runtime_error("oracle: boosting=" + cfg.boosting + " is not restated");
     shrinkage_rate = boost == BOOST_RF ? 1.0 : cfg.learning_rate;
     drop_rand = Random(cfg.drop_seed);
-    if (cfg.zero_as_missing) throw std::runtime_error("oracle: zero_as_missing is not restated");
     feature_rand = Random(cfg.feature_fraction_seed);
     tree_mask.assign(F, 1);
     bagging = (cfg.bagging_freq > 0 && cfg.bagging_fraction < 1.0) || boost == BOOST_GOSS;
@@ -1011,7 +1024,7 @@ class Booster {
         const data_size_t r = sh.indices[b + i];
         const uint32_t bin = d->bin_at(bs.feature, r);
         bool go_left;
-        if (m.missing_type == MISSING_NAN && bin == nan_bin) go_left = bs.default_left;
+        if ((m.missing_type == MISSING_NAN && bin == nan_bin) || (m.missing_type == MISSING_ZERO && bin == m.default_bin)) go_left = bs.default_left;
         else go_left = bin <= bs.threshold;
         if (go_left) sh.tmp_left[nl++] = r; else sh.tmp_right[nr++] = r;
       }
@@ -1206,7 +1219,7 @@ class Booster {
       const int mt = (t.decision_type[node] >> 2) & 3;
       const bool dl = (t.decision_type[node] & 2) != 0;
       bool left;
-      if (mt == MISSING_NAN && bin == static_cast<uint32_t>(m.num_bin - 1)) left = dl;
+      if ((mt == MISSING_NAN && bin == static_cast<uint32_t>(m.num_bin - 1)) || (mt == MISSING_ZERO && bin == m.default_bin)) left = dl;
       else left = bin <= t.threshold_in_bin[node];
       node = left ? t.left_child[node] : t.right_child[node];
     }

@@ -1351,7 +1351,9 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const int f = T.split_feature_inner[i];
       const int dt = T.decision_type[i];
       const FeatureMetaDev fm = fmeta[f];
-      const unsigned nan_bin = (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1) : 256u;
+      // the bin whose rows follow default_left: the NaN bin, or the zero bin under zero_as_missing
+      const unsigned nan_bin = (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1)
+                               : (fm.missing_type == kMissingZero) ? static_cast<unsigned>(fm.default_bin) : 256u;
       uint2 nd;
       nd.x = static_cast<unsigned>(f) | (nan_bin << 14) | (static_cast<unsigned>(T.threshold_in_bin[i]) << 23) | ((dt & 2) ? (1u << 31) : 0u);
       nd.y = (static_cast<unsigned>(T.left_child[i]) & 0xffffu) | (static_cast<unsigned>(T.right_child[i]) << 16);

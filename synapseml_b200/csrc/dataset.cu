@@ -631,7 +631,6 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   LGB_CHECK(ncol > 0, "ncol must be positive");
   LGB_CHECK(c.max_bin >= 2 && c.max_bin <= 255, "max_bin=%d is outside [2, 255] (uint8 bin storage)", c.max_bin);
   LGB_CHECK(c.categorical_feature.empty(), "categorical_feature is not supported by this library yet");
-  LGB_CHECK(!c.zero_as_missing, "zero_as_missing=true is not supported by this library yet");
   ds->device = ResolveDevice(c);
   LGB_CUDA(cudaSetDevice(ds->device));
   ds->num_total_features = ncol;

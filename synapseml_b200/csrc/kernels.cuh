@@ -455,8 +455,13 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   int& s_flag = s_flag_all[sub];
   const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
   const int num_bin = fm.num_bin;
-  const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
-  const int nan_bin = two_scans ? num_bin - 1 : -1;
+  // two scans when the feature has a missing type and more than two bins.  NaN type: the last bin is left out of both scans
+  // (NA_AS_MISSING); Zero type (zero_as_missing): the default bin is neither accumulated nor a threshold (SKIP_DEFAULT_BIN), and the
+  // forward scan starts at bin 1 when the most frequent bin is bin 0 (upstream keeps that bin out of its histogram)
+  const bool zero_type = fm.missing_type == kMissingZero;
+  const bool two_scans = (num_bin > 2 && (fm.missing_type == kMissingNaN || zero_type));
+  const int nan_bin = !two_scans ? -1 : zero_type ? fm.default_bin : num_bin - 1;      // the bin both scans leave out
+  const int fstart = (two_scans && zero_type && fm.most_freq_bin == 0) ? 1 : 0;
   if (b == 0) s_flag = 0;
   // pass 0 (root only): leaf totals = sum of all bins of this feature
   if (root) {
@@ -494,6 +499,9 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     const int tc = __shfl_up_sync(0xffffffffu, pc, o);
     if (lane >= o) { pg += tg; ph += th; pc += tc; }
   }
+  __shared__ long long s_g0_all[kMaxFindSubs], s_h0_all[kMaxFindSubs];
+  __shared__ int s_c0_all[kMaxFindSubs];
+  if (b == 0) { s_g0_all[sub] = gv; s_h0_all[sub] = hv; s_c0_all[sub] = cv; }      // bin 0, which a forward scan from bin 1 leaves out
   if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
   SubSync(sub);
   long long Tg = 0, Th = 0; int Tc = 0;
@@ -506,9 +514,9 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   const double min_gain_shift = gain_shift + P.min_gain_to_split;
   bool splittable = false;
   // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
-  const int top = num_bin - 1 - (two_scans ? 1 : 0);
+  const int top = num_bin - 1 - ((two_scans && !zero_type) ? 1 : 0);
   Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
-  if (b >= 1 && b <= top) {
+  if (b >= 1 && b <= top && b != nan_bin) {
     const long long rgi = Tg - (pg - gv), rhi = Th - (ph - hv);
     double gain = 0.0; int rc; bool ok = true;
     if (QUANT) {
@@ -531,8 +539,8 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   }
   // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
   Cand cf; cf.gain = KMINSCORE; cf.b = -1; cf.sg = 0; cf.sh = 0; cf.cnt = 0;
-  if (two_scans && b <= num_bin - 2) {
-    const long long lgi = pg, lhi = ph;
+  if (two_scans && b >= fstart && b <= num_bin - 2 && b != nan_bin) {
+    const long long lgi = pg - (fstart ? s_g0_all[sub] : 0), lhi = ph - (fstart ? s_h0_all[sub] : 0);
     double gain = 0.0; int lc; bool ok = true;
     if (QUANT) {
       lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
@@ -543,7 +551,7 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
       ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
       if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
     } else {
-      lc = pc;
+      lc = pc - (fstart ? s_c0_all[sub] : 0);
       const double lh = KEPS + static_cast<double>(lhi) * hscale;
       const int rc = num_data - lc;
       const double rh = sum_hessian - lh;
@@ -561,7 +569,7 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
     const bool any = s_flag != 0;
     SplitDev s = EmptySplit(f, fm.real_index);
     s.missing_type = fm.missing_type;
-    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
+    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : zero_type ? fm.default_bin : -1;      // rows of this bin follow default_left
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;
@@ -637,8 +645,10 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
                                              unsigned char* splittable_out, long long* out_tot_g, long long* out_tot_h) {
   const int lane = threadIdx.x & 31;
   const int num_bin = fm.num_bin;
-  const bool two_scans = (num_bin > 2 && fm.missing_type == kMissingNaN);
-  const int nan_bin = two_scans ? num_bin - 1 : -1;
+  const bool zero_type = fm.missing_type == kMissingZero;      // (see BlockFindBest)
+  const bool two_scans = (num_bin > 2 && (fm.missing_type == kMissingNaN || zero_type));
+  const int nan_bin = !two_scans ? -1 : zero_type ? fm.default_bin : num_bin - 1;
+  const int fstart = (two_scans && zero_type && fm.most_freq_bin == 0) ? 1 : 0;
   if (root) {      // the leaf totals = the sum of all bins of this feature
     long long tg = 0, th = 0;
     #pragma unroll
@@ -685,10 +695,15 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
   const long long Tg = __shfl_sync(0xffffffffu, og, 31), Th = __shfl_sync(0xffffffffu, oh, 31);
   const int Tc = __shfl_sync(0xffffffffu, oc, 31);
   og -= lg; oh -= lh; oc -= lc;      // what the lower lanes hold
+  // bin 0 (lane 0's first bin), which a forward scan that starts at bin 1 leaves out
+  long long g0, h0; int c0;
+  masked(0, &g0, &h0, &c0);
+  g0 = __shfl_sync(0xffffffffu, g0, 0); h0 = __shfl_sync(0xffffffffu, h0, 0); c0 = __shfl_sync(0xffffffffu, c0, 0);
+  if (!fstart) { g0 = 0; h0 = 0; c0 = 0; }
   const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
   const double min_gain_shift = gain_shift + P.min_gain_to_split;
   bool splittable = false;
-  const int top = num_bin - 1 - (two_scans ? 1 : 0);
+  const int top = num_bin - 1 - ((two_scans && !zero_type) ? 1 : 0);
   Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
   Cand cf = cr;
   #pragma unroll
@@ -700,7 +715,7 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
     const long long ipg = og, iph = oh;      // inclusive prefix over bins [0, b]
     const int ipc = oc;
     // ---- reverse scan candidate: right = bins [b, top], threshold = b - 1
-    if (b >= 1 && b <= top) {
+    if (b >= 1 && b <= top && b != nan_bin) {
       const long long rgi = Tg - (ipg - gvj), rhi = Th - (iph - hvj);
       double gain = 0.0; int rc; bool ok = true;
       if (QUANT) {
@@ -726,8 +741,8 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
       }
     }
     // ---- forward scan candidate (NaN as missing): left = bins [0, b], threshold = b
-    if (two_scans && b <= num_bin - 2) {
-      const long long lgi = ipg, lhi = iph;
+    if (two_scans && b >= fstart && b <= num_bin - 2 && b != nan_bin) {
+      const long long lgi = ipg - g0, lhi = iph - h0;
       double gain = 0.0; int lcn; bool ok = true;
       if (QUANT) {
         lcn = RoundIntD(static_cast<double>(lhi) * cnt_factor);
@@ -738,7 +753,7 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
         ok = !(lcn < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
         if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
       } else {
-        lcn = ipc;
+        lcn = ipc - c0;
         const double lhh = KEPS + static_cast<double>(lhi) * hscale;
         const int rc = num_data - lcn;
         const double rh = sum_hessian - lhh;
@@ -759,7 +774,7 @@ __device__ __forceinline__ void WarpFindBest(const long long (&g_in)[kBinsPerLan
   if (lane == 0) {
     SplitDev s = EmptySplit(f, fm.real_index);
     s.missing_type = fm.missing_type;
-    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : -1;
+    s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : zero_type ? fm.default_bin : -1;      // rows of this bin follow default_left
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;

@@ -183,15 +183,26 @@ class LightGBMBase:
         every rank hands the part of its rows that falls inside that head to rank 0; the other modes sample rank 0's rows only."""
         if dist is None or self._p["samplingMode"] != "fixed":
             return self.get_sampled_rows(df, total_rows) if rank == 0 else None
+        import torch
         num_samples = min(self.getBinSampleCount(), total_rows)
-        before = int(sum(counts[:rank]))
-        k = int(min(max(num_samples - before, 0), counts[rank]))
-        mine = self.get_sampled_rows(df, k) if k > 0 else None      # "fixed": the first k local rows
-        parts = [None] * dist.get_world_size() if rank == 0 else None
-        dist.gather_object(mine, parts, dst=0)
+        take = []      # rows of every rank that fall inside the first num_samples rows of the global order
+        before = 0
+        for c in counts:
+            take.append(int(min(max(num_samples - before, 0), c)))
+            before += c
+        k = take[rank]
+        mine = np.ascontiguousarray(self.get_sampled_rows(df, k), dtype=np.float64) if k > 0 else None      # "fixed": the first k local rows
         if rank != 0:
+            if k > 0:
+                dist.send(torch.from_numpy(mine), dst=0)      # a plain buffer: no pickling of what can be gigabytes (C5: 200k x 2000 f64)
             return None
-        parts = [p for p in parts if p is not None]
+        ncol = mine.shape[1]
+        parts = [mine]
+        for r in range(1, len(counts)):
+            if take[r] > 0:
+                buf = torch.empty((take[r], ncol), dtype=torch.float64)
+                dist.recv(buf, src=r)
+                parts.append(buf.numpy())
         return parts[0] if len(parts) == 1 else np.concatenate(parts)
 
     def preprocess_data(self, df):

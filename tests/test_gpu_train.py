@@ -224,3 +224,35 @@ def test_both_split_search_forms_give_the_same_model(native, monkeypatch, mode):
             nb.free()
             nd.free()
         assert models[0] == models[1]
+
+
+@pytest.mark.parametrize("mode", ["quantized", "float"])
+def test_zero_as_missing(native, oracle, mode):
+    """zeroAsMissing (LightGBMParams.scala:176): zeros and NaNs are the missing value; the split search leaves the zero bin out of
+    both scans (SKIP_DEFAULT_BIN), rows of that bin follow default_left in the partition, the score pass and the predictor."""
+    rng = np.random.Generator(np.random.PCG64(11))
+    n = 40000
+    X = rng.standard_normal((n, 8))
+    X[:, 0] = np.where(rng.random(n) < 0.5, 0.0, rng.exponential(1.0, n))                 # zero is the most frequent bin and bin 0
+    X[:, 1] = np.where(rng.random(n) < 0.3, 0.0, rng.standard_normal(n))                  # zero in the middle of the range
+    X[:, 2] = np.where(rng.random(n) < 0.2, np.nan, np.where(rng.random(n) < 0.3, 0.0, rng.standard_normal(n) - 2.0))   # NaN counts as zero
+    X[:, 3] = np.where(rng.random(n) < 0.85, -1.5, rng.standard_normal(n))                # most frequent bin 0 is NOT the zero bin
+    X[:, 4] = rng.integers(0, 3, n).astype(np.float64)
+    z = 1.2 * (X[:, 0] == 0) - 0.8 * (np.nan_to_num(X[:, 1]) == 0) + 0.7 * np.nan_to_num(X[:, 2]) + 0.5 * X[:, 3] + 0.4 * X[:, 5]
+    y = (rng.random(n) < 1 / (1 + np.exp(-z))).astype(np.float32)
+    params = "objective=binary num_leaves=31 max_bin=63 min_data_in_leaf=20 zero_as_missing=true verbosity=-1"
+    if mode == "quantized":
+        params += " use_quantized_grad=true stochastic_rounding=false"
+    nd, nb, ob = train_both(oracle, X, y, params, 10, micro_batches=(4096,))
+    ms, mo = nb.model(), ob.save_model_to_string()
+    m = TextModel(ms)
+    if mode == "quantized":
+        assert strip_parameters(ms) == strip_parameters(mo)
+        assert np.array_equal(nb.scores(), ob.scores())
+    else:
+        assert m.structure()[:4] == TextModel(mo).structure()[:4]
+        assert np.abs(nb.scores() - ob.scores()).max() <= FLOAT_RTOL * np.abs(ob.scores()).max()
+    assert any(((t.decision_type >> 2) & 3 == 1).any() for t in m.trees if t.num_leaves > 1)      # Zero-typed splits were exercised
+    assert np.allclose(m.predict_raw(X), nb.scores(), rtol=0, atol=1e-12)                          # bins and raw values route alike
+    nb.free()
+    nd.free()
