@@ -332,6 +332,8 @@ struct Config {
         objective == "l2_root" || objective == "root_mean_squared_error" || objective == "rmse")
       objective = "regression";
     if (objective == "softmax") objective = "multiclass";
+    if (objective == "l1" || objective == "mean_absolute_error" || objective == "mae") objective = "regression_l1";
+    if (objective == "mean_absolute_percentage_error") objective = "mape";
   }
 };
 

@@ -251,6 +251,40 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
   return splittable;
 }
 
+// PercentileFun / WeightedPercentileFun (upstream src/objective/regression_objective.hpp), on a copy of the data.  alpha_f: the
+// quantile objective keeps alpha as a float, so (1.0f - alpha) * cnt is float arithmetic there; L1 uses the double 0.5.
+template <typename T>
+inline T PercentileOf(std::vector<T> data, double alpha, bool alpha_is_float) {
+  const int cnt = static_cast<int>(data.size());
+  if (cnt <= 1) return data[0];
+  const double float_pos = alpha_is_float ? static_cast<double>((1.0f - static_cast<float>(alpha)) * cnt) : (1.0f - alpha) * cnt;
+  const int pos = static_cast<int>(float_pos);
+  std::sort(data.begin(), data.end(), std::greater<T>());      // descending: [pos - 1] is the pos-th largest
+  if (pos < 1) return data[0];
+  if (pos >= cnt) return data[cnt - 1];
+  const double bias = float_pos - pos;
+  const T v1 = data[pos - 1], v2 = data[pos];
+  return static_cast<T>(v1 - (v1 - v2) * bias);
+}
+template <typename T1, typename T2>
+inline T1 WeightedPercentileOf(const std::vector<T1>& data, const std::vector<T2>& weight, double alpha, bool alpha_is_float) {
+  const int cnt = static_cast<int>(data.size());
+  if (cnt <= 1) return data[0];
+  std::vector<int> idx(cnt);
+  for (int i = 0; i < cnt; ++i) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return data[a] < data[b]; });
+  std::vector<T2> cdf(cnt);
+  cdf[0] = weight[idx[0]];
+  for (int i = 1; i < cnt; ++i) cdf[i] = cdf[i - 1] + weight[idx[i]];
+  const T2 threshold = alpha_is_float ? static_cast<T2>(cdf[cnt - 1] * static_cast<float>(alpha)) : static_cast<T2>(cdf[cnt - 1] * alpha);
+  size_t pos = std::upper_bound(cdf.begin(), cdf.end(), threshold) - cdf.begin();
+  pos = std::min(pos, static_cast<size_t>(cnt - 1));
+  if (pos == 0 || pos == static_cast<size_t>(cnt - 1)) return data[idx[pos]];
+  const T1 v1 = data[idx[pos - 1]], v2 = data[idx[pos]];
+  if (cdf[pos + 1] - cdf[pos] >= 1.0f) return static_cast<T1>((threshold - cdf[pos]) / (cdf[pos + 1] - cdf[pos]) * (v2 - v1) + v1);
+  return static_cast<T1>(v2);
+}
+
 struct Shard {
   const Dataset* ds = nullptr;
   int64_t row_offset = 0;                 // global row id of local row 0 (for the stochastic-rounding stream)
@@ -276,7 +310,9 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE } obj = OBJ_L2;
+  bool RenewsLeaves() const { return obj == OBJ_L1 || obj == OBJ_QUANTILE || obj == OBJ_MAPE; }      // IsRenewTreeOutput
+  std::vector<std::vector<label_t>> label_weight;      // mape: per shard, 1 / max(1, |label|) (* weight)
   enum Boost { BOOST_GBDT, BOOST_RF, BOOST_DART, BOOST_GOSS } boost = BOOST_GBDT;
   double shrinkage_rate = 0.1;             // learning_rate, except under DART, which rescales it by the number of dropped trees
   std::vector<double> rf_init_scores;      // RF: the automatic initial scores (never added to the scores; every tree carries them)
@@ -288,7 +324,7 @@ class Booster {
   int cur_class = 0;
   std::vector<double> class_init_probs;    // multiclass: (weighted) share of every label over all machines
   std::vector<char> class_need_train;
-  bool IsPointRegression() const { return obj == OBJ_L2 || (obj >= OBJ_HUBER && obj <= OBJ_TWEEDIE); }
+  bool IsPointRegression() const { return obj == OBJ_L2 || (obj >= OBJ_HUBER && obj <= OBJ_TWEEDIE) || RenewsLeaves(); }
   bool LogLink() const { return obj == OBJ_POISSON || obj == OBJ_GAMMA || obj == OBJ_TWEEDIE; }
   bool need_train = true;
   double label_weights[2] = {1.0, 1.0};
@@ -436,6 +472,35 @@ class Booster {
     }
   }
 
+  // SerialTreeLearner::RenewTreeOutput with the objective's RenewTreeOutput (l1 / quantile / mape): every leaf's output becomes the
+  // (weighted) percentile of label - score over the leaf's rows on each machine; machines that hold rows of the leaf are averaged.
+  void RenewTreeOutput(Tree* tree) {
+    const double a = obj == OBJ_QUANTILE ? cfg.alpha : 0.5;
+    const bool af = obj == OBJ_QUANTILE;
+    for (int l = 0; l < tree->num_leaves; ++l) {
+      double acc = 0.0;
+      int nworkers = 0;
+      for (size_t s = 0; s < shards.size(); ++s) {
+        Shard& sh = shards[s];
+        const data_size_t b = sh.leaf_begin[l], n = sh.leaf_count[l];
+        if (n <= 0) continue;
+        std::vector<double> res(n);
+        std::vector<label_t> w(n);
+        for (data_size_t i = 0; i < n; ++i) {
+          const data_size_t r = sh.indices[b + i];
+          res[i] = static_cast<double>(sh.ds->label[r]) - sh.score[r];
+          if (obj == OBJ_MAPE) w[i] = label_weight[s][r]; else if (has_weights) w[i] = sh.ds->weight[r];
+        }
+        double out;
+        if (obj == OBJ_MAPE || has_weights) out = WeightedPercentileOf<double, label_t>(res, w, a, af);
+        else out = PercentileOf<double>(res, a, af);
+        acc += out;
+        ++nworkers;
+      }
+      tree->leaf_value[l] = shards.size() > 1 ? acc / nworkers : acc;
+    }
+  }
+
   // ScoreUpdater::AddScore(tree, class): every row walks the tree over its bins
   void AddTreeToScores(const Tree& t, int k) {
     for (auto& sh : shards) {
@@ -543,6 +608,19 @@ class Booster {
       obj = cfg.objective == "poisson" ? OBJ_POISSON : cfg.objective == "gamma" ? OBJ_GAMMA : OBJ_TWEEDIE;
       for (auto& sh : shards) for (float l : sh.ds->label)      // RegressionPoissonLoss::Init / Gamma: label domain
         if (l < 0.0f || (obj == OBJ_GAMMA && l <= 0.0f)) throw std::runtime_error("oracle: " + cfg.objective + " needs non-negative labels");
+    } else if (cfg.objective == "regression_l1" || cfg.objective == "quantile" || cfg.objective == "mape") {
+      obj = cfg.objective == "regression_l1" ? OBJ_L1 : cfg.objective == "quantile" ? OBJ_QUANTILE : OBJ_MAPE;
+      if (obj == OBJ_MAPE) {      // RegressionMAPELOSS::Init
+        for (auto& sh : shards) {
+          const Dataset* d = sh.ds;
+          std::vector<label_t> lw(d->num_data);
+          for (int64_t i = 0; i < d->num_data; ++i) {
+            lw[i] = 1.0f / std::max(1.0f, std::fabs(d->label[i]));
+            if (has_weights) lw[i] = lw[i] * d->weight[i];
+          }
+          label_weight.push_back(std::move(lw));
+        }
+      }
     } else if (cfg.objective == "multiclass") {
       // MulticlassSoftmax::Init (upstream src/objective/multiclass_objective.hpp)
       obj = OBJ_MULTICLASS;
@@ -643,6 +721,23 @@ class Booster {
       pavg = std::max<double>(pavg, kEpsilon);
       return std::log(pavg / (1.0f - pavg)) / cfg.sigmoid;
     }
+    if (RenewsLeaves()) {
+      // RegressionL1loss / Quantile / MAPE::BoostFromScore: the (weighted) percentile of the machine's own labels; the mean over
+      // machines is taken by ObtainAutomaticInitialScore (GlobalSyncUpByMean), so the caller must not average again
+      double acc = 0.0;
+      for (size_t s = 0; s < shards.size(); ++s) {
+        const Dataset* d = shards[s].ds;
+        std::vector<label_t> lab(d->label.begin(), d->label.begin() + d->num_data);
+        const double a = obj == OBJ_QUANTILE ? cfg.alpha : 0.5;
+        const bool af = obj == OBJ_QUANTILE;
+        label_t v;
+        if (obj == OBJ_MAPE) v = WeightedPercentileOf<label_t, label_t>(lab, label_weight[s], 0.5, false);
+        else if (has_weights) v = WeightedPercentileOf<label_t, label_t>(lab, std::vector<label_t>(d->weight.begin(), d->weight.begin() + d->num_data), a, af);
+        else v = PercentileOf<label_t>(lab, a, af);
+        acc += static_cast<double>(v);
+      }
+      return acc / static_cast<double>(shards.size());
+    }
     if (IsPointRegression()) {
       for (auto& sh : shards) {
         const Dataset* d = sh.ds;
@@ -693,6 +788,29 @@ class Booster {
         }
       } else if (obj == OBJ_CUSTOM) {
         throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
+      } else if (RenewsLeaves()) {
+        // RegressionL1loss / RegressionQuantileloss / RegressionMAPELOSS::GetGradients
+        const score_t alpha_f = static_cast<score_t>(cfg.alpha);
+        const std::vector<label_t>* lw = obj == OBJ_MAPE ? &label_weight[s] : nullptr;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+          if (obj == OBJ_L1) {
+            const double diff = sh.score[i] - d->label[i];
+            const int sg = (diff > 0) - (diff < 0);
+            if (!has_weights) { sh.grad[i] = static_cast<score_t>(sg); sh.hess[i] = 1.0f; }
+            else { sh.grad[i] = static_cast<score_t>(sg * d->weight[i]); sh.hess[i] = d->weight[i]; }
+          } else if (obj == OBJ_QUANTILE) {
+            const score_t delta = static_cast<score_t>(sh.score[i] - d->label[i]);
+            const score_t g = delta >= 0 ? (1.0f - alpha_f) : -alpha_f;
+            if (!has_weights) { sh.grad[i] = g; sh.hess[i] = 1.0f; }
+            else { sh.grad[i] = static_cast<score_t>(g * d->weight[i]); sh.hess[i] = static_cast<score_t>(d->weight[i]); }
+          } else {
+            const double diff = sh.score[i] - d->label[i];
+            const int sg = (diff > 0) - (diff < 0);
+            sh.grad[i] = static_cast<score_t>(sg * (*lw)[i]);
+            sh.hess[i] = has_weights ? d->weight[i] : 1.0f;
+          }
+        }
       } else if (obj != OBJ_LAMBDARANK) {
         // regression_objective.hpp: Huber (alpha), Fair (fair_c), Poisson (poisson_max_delta_step), Gamma, Tweedie (rho); exp is the
         // software exp shared with the CUDA library
@@ -842,7 +960,7 @@ class Booster {
         if (ah > max_h) max_h = ah;
       }
     }
-    const bool const_hess = (obj == OBJ_L2 && !has_weights);
+    const bool const_hess = ((obj == OBJ_L2 || obj == OBJ_L1 || obj == OBJ_QUANTILE) && !has_weights) || obj == OBJ_MAPE;      // IsConstantHessian
     grad_scale = max_g / static_cast<double>(cfg.num_grad_quant_bins / 2);
     hess_scale = const_hess ? max_h : max_h / static_cast<double>(cfg.num_grad_quant_bins);
     const double inv_g = 1.0f / grad_scale, inv_h = 1.0f / hess_scale;
@@ -1109,6 +1227,7 @@ class Booster {
       if (train_this && F > 0) tree = TrainTree();
       if (tree->num_leaves > 1) {
         should_continue = true;
+        if (RenewsLeaves()) RenewTreeOutput(tree.get());
         tree->Shrinkage(shrinkage_rate);
         for (auto& sh : shards) {
           for (int l = 0; l < tree->num_leaves; ++l) {
@@ -1231,6 +1350,7 @@ class Booster {
     if (obj == OBJ_L2) return "regression";
     if (obj == OBJ_CUSTOM) return "";
     if (obj == OBJ_MULTICLASS) return "multiclass num_class:" + std::to_string(K);
+    if (RenewsLeaves()) return cfg.objective;
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }

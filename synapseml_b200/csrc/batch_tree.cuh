@@ -1306,6 +1306,96 @@ __global__ void k_fill_double(double* p, long long n, double v) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) p[i] = v;
 }
 
+// ------------------------------------------------------------------------------------------------ leaf re-fit (l1 / quantile / mape)
+// SerialTreeLearner::RenewTreeOutput with the objective's RenewTreeOutput (upstream regression_objective.hpp): once the tree is
+// finished, every leaf's output becomes the (weighted) percentile of label - score over the leaf's rows.  Three steps on the
+// device: the residuals (and weights) of the leaves' rows are gathered leaf after leaf (k_renew_collect; the offsets come from the
+// node table), sorted per leaf (CUB segmented radix sort, stable), and one warp per leaf evaluates PercentileFun /
+// WeightedPercentileFun on its sorted segment (k_renew_pick).
+__global__ void k_renew_offsets(const NodeDev* __restrict__ nodes, const int* __restrict__ avail, const BatchCtrl* __restrict__ ctrl, int L,
+                                int* __restrict__ off /*[L + 1]*/) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const int nl = (ctrl->done && !ctrl->abort) ? ctrl->num_leaves : 0;
+  int o = 0;
+  for (int l = 0; l < L; ++l) {
+    off[l] = o;
+    if (l < nl && nl > 1) o += nodes[avail[l]].count;
+  }
+  off[L] = o;
+}
+template <int ES>
+__global__ void k_renew_collect(const NodeDev* __restrict__ nodes, const int* __restrict__ avail, const BatchCtrl* __restrict__ ctrl,
+                                const int* __restrict__ off, const int* __restrict__ idx0, const int* __restrict__ idx1,
+                                const float* __restrict__ label, const double* __restrict__ score, const float* __restrict__ weight,
+                                double* __restrict__ res, float* __restrict__ wout) {
+  const int l = blockIdx.x;
+  if (!ctrl->done || ctrl->abort || l >= ctrl->num_leaves || ctrl->num_leaves <= 1) return;
+  const NodeDev& nd = nodes[avail[l]];
+  const int* idx = nd.buf == 0 ? idx0 : idx1;
+  const int o = off[l];
+  for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < nd.count; p += gridDim.y * blockDim.x) {
+    const int row = idx[static_cast<size_t>(nd.begin + p) * ES];
+    res[o + p] = static_cast<double>(label[row]) - score[row];
+    if (weight != nullptr) wout[o + p] = weight[row];
+  }
+}
+// sorted: the leaf's residuals ascending (and their weights).  alpha_is_float: the quantile objective keeps alpha as a float, so
+// (1.0f - alpha) * cnt is float arithmetic there; l1 / mape use the double 0.5.
+__global__ void k_renew_pick(const BatchCtrl* __restrict__ ctrl, const int* __restrict__ off, const double* __restrict__ sorted,
+                             const float* __restrict__ wsorted, double alpha, int alpha_is_float, double* __restrict__ leaf_value,
+                             double* __restrict__ out /*[2][L]: value, has rows*/, int L) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= L) return;
+  out[l] = 0.0; out[L + l] = 0.0;
+  if (!ctrl->done || ctrl->abort || l >= ctrl->num_leaves || ctrl->num_leaves <= 1) return;
+  const int cnt = off[l + 1] - off[l];
+  if (cnt <= 0) { leaf_value[l] = 0.0; return; }      // (data-parallel: another machine holds this leaf's rows)
+  const double* d = sorted + off[l];
+  double v;
+  if (cnt <= 1) {
+    v = d[0];
+  } else if (wsorted == nullptr) {
+    // PercentileFun: with the data DEscending, [pos - 1] and [pos]; here ascending, so [cnt - pos] and [cnt - pos - 1]
+    const double float_pos = alpha_is_float ? static_cast<double>((1.0f - static_cast<float>(alpha)) * cnt) : (1.0f - alpha) * cnt;
+    const int pos = static_cast<int>(float_pos);
+    if (pos < 1) v = d[cnt - 1];
+    else if (pos >= cnt) v = d[0];
+    else {
+      const double bias = float_pos - pos;
+      const double v1 = d[cnt - pos], v2 = d[cnt - pos - 1];
+      v = v1 - (v1 - v2) * bias;
+    }
+  } else {
+    // WeightedPercentileFun: float running sums in sorted order (sequential, as upstream accumulates them)
+    const float* w = wsorted + off[l];
+    float total = w[0];
+    for (int i = 1; i < cnt; ++i) total = total + w[i];
+    const float threshold = alpha_is_float ? static_cast<float>(total * static_cast<float>(alpha)) : static_cast<float>(total * alpha);
+    // pos = upper_bound(cdf, threshold): the first i with cdf[i] > threshold
+    float cdf = 0.0f, cdf_pos = 0.0f;
+    int pos = cnt;
+    for (int i = 0; i < cnt; ++i) {
+      cdf = (i == 0) ? w[0] : cdf + w[i];
+      if (cdf > threshold) { pos = i; cdf_pos = cdf; break; }
+    }
+    pos = min(pos, cnt - 1);
+    if (pos == 0 || pos == cnt - 1) {
+      v = d[pos];
+    } else {
+      const double v1 = d[pos - 1], v2 = d[pos];
+      const float cdf_next = cdf_pos + w[pos + 1];
+      if (cdf_next - cdf_pos >= 1.0f) v = static_cast<double>((threshold - cdf_pos) / (cdf_next - cdf_pos)) * (v2 - v1) + v1;
+      else v = v2;
+    }
+  }
+  leaf_value[l] = v;
+  out[l] = v; out[L + l] = 1.0;
+}
+__global__ void k_set_leaf_values(double* __restrict__ leaf_value, const double* __restrict__ v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) leaf_value[i] = v[i];
+}
+
 // ------------------------------------------------------------------------------------------------ K8 + K3 fused
 // Applies the finished tree to the training scores by walking it with every row's bins (row-major records, streamed once)
 // instead of going through the leaves' index ranges, and — for the row-wise objectives — computes the next iteration's

@@ -1,5 +1,7 @@
 #include "booster.h"
 
+#include <cub/device/device_segmented_radix_sort.cuh>
+
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -112,7 +114,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   lp_.num_leaves = cfg_.num_leaves; lp_.num_features = F_;
   lp_.quantized = cfg_.use_quantized_grad; lp_.dp = net_->active();
   lp_.num_grad_quant_bins = cfg_.num_grad_quant_bins; lp_.stochastic_rounding = cfg_.stochastic_rounding;
-  lp_.const_hessian = (obj_ == kL2 && !has_weights_);
+  lp_.const_hessian = ((obj_ == kL2 || obj_ == kL1 || obj_ == kQuantile) && !has_weights_) || obj_ == kMape;      // IsConstantHessian
   lp_.seed = static_cast<unsigned int>(cfg_.seed);
   // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
   // search's last unit does, as for wide data)
@@ -457,6 +459,17 @@ void Booster::InitObjective() {
       LGB_CHECK(acc[0] == 0.0, "objective=%s needs %s labels", o.c_str(), obj_ == kGamma ? "positive" : "non-negative");
       LGB_CHECK(acc[1] > 0.0, "objective=%s: the sum of the labels is zero", o.c_str());
     }
+  } else if (cfg_.objective == "regression_l1" || cfg_.objective == "quantile" || cfg_.objective == "mape") {
+    obj_ = cfg_.objective == "regression_l1" ? kL1 : cfg_.objective == "quantile" ? kQuantile : kMape;
+    if (obj_ == kMape) {      // RegressionMAPELOSS::Init: label_weight = 1 / max(1, |label|) (* weight)
+      label_weight_.resize(n_);
+      for (int64_t i = 0; i < n_; ++i) {
+        label_weight_[i] = 1.0f / std::max(1.0f, std::fabs(label[i]));
+        if (has_weights_) label_weight_[i] = label_weight_[i] * ds_->weight[i];
+      }
+      d_label_weight_.Alloc(std::max<int64_t>(n_, 1));
+      LGB_CUDA(cudaMemcpy(d_label_weight_.p, label_weight_.data(), sizeof(float) * n_, cudaMemcpyHostToDevice));
+    }
   } else if (cfg_.objective == "multiclass") {
     // MulticlassSoftmax::Init (upstream multiclass_objective.hpp): label shares over all machines, classes that never / always occur
     obj_ = kMulticlass;
@@ -480,7 +493,7 @@ void Booster::InitObjective() {
   } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
     obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, regression, lambdarank, custom)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
   }
 }
 
@@ -511,9 +524,10 @@ void Booster::ComputeGradients(const double* score_override) {
   } else if (obj_ == kL2) {
     k_grad_l2<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
   } else if (obj_ >= kHuber) {
-    const double p0 = obj_ == kHuber ? cfg_.alpha : obj_ == kFair ? cfg_.fair_c : obj_ == kPoisson ? SoftExp(cfg_.poisson_max_delta_step)
-                      : cfg_.tweedie_variance_power;
-    k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0);
+    const double p0 = (obj_ == kHuber || obj_ == kQuantile) ? cfg_.alpha : obj_ == kFair ? cfg_.fair_c
+                      : obj_ == kPoisson ? SoftExp(cfg_.poisson_max_delta_step) : cfg_.tweedie_variance_power;
+    k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0,
+                                            d_label_weight_.p);
   } else {
     LambdarankArgs a;
     a.score = score; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p;
@@ -854,13 +868,18 @@ void Booster::TrainTree(HostTree* out) {
   int rounds = last_rounds_ > 0 ? std::min(L - 1, last_rounds_ + round_slack_) : std::min(L - 1, (L - 1) / 2 + 2);
   rounds = std::max(rounds, 1);
   int total = 0;
+  const bool renew = RenewsLeaves();
   while (true) {
     EnqueueRounds(rounds);
     LGB_CUDA(cudaEventRecord(ev_rounds_done_, stream_));
-    ProfBegin("score_update"); UpdateScores(); ProfEnd();      // does nothing on the device unless the tree is finished
+    // (l1 / quantile / mape: the leaf values are re-fit before the tree may enter the scores)
+    if (!renew) { ProfBegin("score_update"); UpdateScores(); ProfEnd(); }      // does nothing on the device unless the tree is finished
     total += rounds;
     LGB_CUDA(cudaGetLastError());
-    if (FetchTree(out)) break;
+    if (FetchTree(out)) {
+      if (renew) { RenewTreeOutput(out); ProfBegin("score_update"); UpdateScores(); ProfEnd(); }
+      break;
+    }
     ++refetches_;
     LGB_CHECK(total < 2 * L, "tree growth did not finish");   // cannot happen: every round commits at least one split
     rounds = std::min(L - 1, 2);
@@ -879,6 +898,105 @@ void Booster::AbortPeers() {
   cudaSetDevice(device_);
   k_peer_abort<<<1, 32, 0, copy_stream_>>>(peers_);
   cudaStreamSynchronize(copy_stream_);
+}
+
+// BoostFromScore of l1 / quantile / mape: PercentileFun / WeightedPercentileFun (upstream regression_objective.hpp) over this
+// machine's labels, on the host (once per fit).
+namespace {
+template <typename T>
+T HostPercentile(std::vector<T> data, double alpha, bool alpha_is_float) {
+  const int cnt = static_cast<int>(data.size());
+  if (cnt <= 1) return data[0];
+  const double float_pos = alpha_is_float ? static_cast<double>((1.0f - static_cast<float>(alpha)) * cnt) : (1.0f - alpha) * cnt;
+  const int pos = static_cast<int>(float_pos);
+  if (pos < 1) return *std::max_element(data.begin(), data.end());
+  if (pos >= cnt) return *std::min_element(data.begin(), data.end());
+  const double bias = float_pos - pos;
+  std::nth_element(data.begin(), data.begin() + (pos - 1), data.end(), std::greater<T>());      // [pos - 1]: the pos-th largest
+  const T v1 = data[pos - 1];
+  const T v2 = *std::max_element(data.begin() + pos, data.end());
+  return static_cast<T>(v1 - (v1 - v2) * bias);
+}
+template <typename T1, typename T2>
+T1 HostWeightedPercentile(const std::vector<T1>& data, const std::vector<T2>& weight, double alpha, bool alpha_is_float) {
+  const int cnt = static_cast<int>(data.size());
+  if (cnt <= 1) return data[0];
+  std::vector<int> idx(cnt);
+  for (int i = 0; i < cnt; ++i) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return data[a] < data[b]; });
+  std::vector<T2> cdf(cnt);
+  cdf[0] = weight[idx[0]];
+  for (int i = 1; i < cnt; ++i) cdf[i] = cdf[i - 1] + weight[idx[i]];
+  const T2 threshold = alpha_is_float ? static_cast<T2>(cdf[cnt - 1] * static_cast<float>(alpha)) : static_cast<T2>(cdf[cnt - 1] * alpha);
+  size_t pos = std::upper_bound(cdf.begin(), cdf.end(), threshold) - cdf.begin();
+  pos = std::min(pos, static_cast<size_t>(cnt - 1));
+  if (pos == 0 || pos == static_cast<size_t>(cnt - 1)) return data[idx[pos]];
+  const T1 v1 = data[idx[pos - 1]], v2 = data[idx[pos]];
+  if (cdf[pos + 1] - cdf[pos] >= 1.0f) return static_cast<T1>((threshold - cdf[pos]) / (cdf[pos + 1] - cdf[pos]) * (v2 - v1) + v1);
+  return static_cast<T1>(v2);
+}
+}  // namespace
+
+double Booster::PercentileInitScore() const {
+  std::vector<float> lab(ds_->label.begin(), ds_->label.begin() + n_);
+  const double a = obj_ == kQuantile ? cfg_.alpha : 0.5;
+  const bool af = obj_ == kQuantile;
+  if (obj_ == kMape) return static_cast<double>(HostWeightedPercentile<float, float>(lab, label_weight_, 0.5, false));
+  if (has_weights_) return static_cast<double>(HostWeightedPercentile<float, float>(lab, std::vector<float>(ds_->weight.begin(), ds_->weight.begin() + n_), a, af));
+  return static_cast<double>(HostPercentile<float>(lab, a, af));
+}
+
+// SerialTreeLearner::RenewTreeOutput for the finished tree (device: batch_tree.cuh "leaf re-fit"); with several machines the
+// outputs of the machines that hold rows of a leaf are averaged (Network::GlobalSum of outputs and of the has-rows flags).
+void Booster::RenewTreeOutput(HostTree* tree) {
+  const int L = cfg_.num_leaves;
+  const int nl = tree->num_leaves;
+  if (nl <= 1) return;
+  const bool weighted = has_weights_ || obj_ == kMape;
+  const float* w = obj_ == kMape ? d_label_weight_.p : has_weights_ ? ds_->d_weight.p : nullptr;
+  d_renew_off_.Reserve(L + 1);
+  d_renew_out_.Reserve(2 * static_cast<size_t>(L));
+  for (int k = 0; k < 2; ++k) { d_renew_res_[k].Reserve(n_); if (weighted) d_renew_w_[k].Reserve(n_); }
+  k_renew_offsets<<<1, 32, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, L, d_renew_off_.p);
+  const dim3 cgrid(nl, std::max(1, std::min(64, static_cast<int>(n_ / (1024 * static_cast<int64_t>(nl)) + 1))));
+  if (idx_es_ == 2)
+    k_renew_collect<2><<<cgrid, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_renew_off_.p, d_idx_[0].p, d_idx_[1].p, ds_->d_label.p,
+                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p);
+  else
+    k_renew_collect<4><<<cgrid, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_renew_off_.p, d_idx_[0].p, d_idx_[1].p, ds_->d_label.p,
+                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p);
+  size_t tmp = 0;
+  const int n = static_cast<int>(n_);
+  if (weighted)
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, d_renew_res_[0].p, d_renew_res_[1].p, d_renew_w_[0].p, d_renew_w_[1].p, n, nl,
+                                                      d_renew_off_.p, d_renew_off_.p + 1, 0, 64, stream_));
+  else
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortKeys(nullptr, tmp, d_renew_res_[0].p, d_renew_res_[1].p, n, nl, d_renew_off_.p,
+                                                     d_renew_off_.p + 1, 0, 64, stream_));
+  d_cub_tmp_.Reserve(tmp);
+  tmp = d_cub_tmp_.n;
+  if (weighted)
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortPairs(d_cub_tmp_.p, tmp, d_renew_res_[0].p, d_renew_res_[1].p, d_renew_w_[0].p, d_renew_w_[1].p, n, nl,
+                                                      d_renew_off_.p, d_renew_off_.p + 1, 0, 64, stream_));
+  else
+    LGB_CUDA(cub::DeviceSegmentedRadixSort::SortKeys(d_cub_tmp_.p, tmp, d_renew_res_[0].p, d_renew_res_[1].p, n, nl, d_renew_off_.p,
+                                                     d_renew_off_.p + 1, 0, 64, stream_));
+  k_renew_pick<<<CeilDiv(L, 64), 64, 0, stream_>>>(d_ctrl_, d_renew_off_.p, d_renew_res_[1].p, weighted ? d_renew_w_[1].p : nullptr,
+                                                   obj_ == kQuantile ? cfg_.alpha : 0.5, obj_ == kQuantile ? 1 : 0, tree_dev_.leaf_value,
+                                                   d_renew_out_.p, L);
+  std::vector<double> out(2 * static_cast<size_t>(L));
+  LGB_CUDA(cudaMemcpyAsync(out.data(), d_renew_out_.p, sizeof(double) * 2 * L, cudaMemcpyDeviceToHost, stream_));
+  LGB_CUDA(cudaStreamSynchronize(stream_));
+  LGB_CUDA(cudaGetLastError());
+  launches_ += 4;
+  if (net_->active()) {
+    net_->HostAllReduceSum(out.data(), 2 * L);
+    for (int l = 0; l < nl; ++l) out[l] = out[L + l] > 0.0 ? out[l] / out[L + l] : 0.0;
+    LGB_CUDA(cudaMemcpyAsync(d_renew_out_.p, out.data(), sizeof(double) * nl, cudaMemcpyHostToDevice, stream_));
+    k_set_leaf_values<<<CeilDiv(nl, 64), 64, 0, stream_>>>(tree_dev_.leaf_value, d_renew_out_.p, nl);
+    LGB_CUDA(cudaStreamSynchronize(stream_));
+  }
+  for (int l = 0; l < nl; ++l) tree->leaf_value[l] = out[l];
 }
 
 // Copies the control block and the tree arrays back; false when the tree is not finished yet (more rounds are needed).
@@ -1007,6 +1125,11 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     double v;
     if (obj_ == kMulticlass) {
       v = std::log(std::max<double>(kEps, class_init_probs_[cls_]));
+    } else if (RenewsLeaves()) {
+      // the (weighted) percentile of this machine's labels; ObtainAutomaticInitialScore then takes the mean over machines
+      double acc = PercentileInitScore();
+      net_->HostAllReduceSum(&acc, 1);
+      v = acc / net_->world();
     } else {
       double sums[2];
       BoostFromScoreLocalSums(&sums[0], &sums[1]);
@@ -1156,7 +1279,7 @@ ModelHeader Booster::MakeHeader() const {
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
   else if (obj_ == kL2) h.objective = "regression";
   else if (obj_ == kMulticlass) { h.objective = "multiclass num_class:" + std::to_string(K_); h.num_class = K_; h.num_tree_per_iteration = K_; }
-  else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
+  else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie / regression_l1 / quantile / mape: the name alone
   else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
   h.average_output = boost_ == kRF;
@@ -1215,6 +1338,9 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     LGB_CHECK(K_ >= 2 && K_ == loaded_header_.num_class, "Model string: multiclass needs num_tree_per_iteration == num_class >= 2");
   } else if (o == "huber" || o == "fair" || o == "poisson" || o == "gamma" || o == "tweedie") {
     obj_ = o == "huber" ? kHuber : o == "fair" ? kFair : o == "poisson" ? kPoisson : o == "gamma" ? kGamma : kTweedie;
+    cfg_.objective = o;
+  } else if (o == "regression_l1" || o == "quantile" || o == "mape") {
+    obj_ = o == "regression_l1" ? kL1 : o == "quantile" ? kQuantile : kMape;      // identity output, as plain regression
     cfg_.objective = o;
   } else if (o.empty() || o.rfind("custom", 0) == 0) {
     obj_ = kCustom;      // trained with caller-supplied gradients: predictions are raw scores

@@ -170,8 +170,16 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass } obj_ = kL2;
-  bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie); }
+  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass, kL1, kQuantile, kMape } obj_ = kL2;
+  bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie) || RenewsLeaves(); }
+  // l1 / quantile / mape (upstream IsRenewTreeOutput): every leaf's output is re-fit as a percentile of the residuals of its rows
+  bool RenewsLeaves() const { return obj_ == kL1 || obj_ == kQuantile || obj_ == kMape; }
+  void RenewTreeOutput(HostTree* tree);
+  double PercentileInitScore() const;
+  std::vector<float> label_weight_;          // mape: 1 / max(1, |label|) [* weight]
+  DevBuf<float> d_label_weight_, d_renew_w_[2];
+  DevBuf<double> d_renew_res_[2], d_renew_out_;
+  DevBuf<int> d_renew_off_;
   // boosting type (upstream src/boosting/{gbdt,rf,dart,goss}.hpp)
   enum Boost { kGBDT, kRF, kDART, kGOSS } boost_ = kGBDT;
   double shrinkage_rate_ = 0.1;             // learning_rate; DART rescales it by the number of dropped trees, RF uses 1

@@ -18,7 +18,7 @@ namespace lgb {
 namespace {
 constexpr int kNumSms = 148;
 enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
-       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12 };   // (Booster has its own kL2: distinct names)
+       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -52,6 +52,9 @@ void Booster::InitMetrics() {
     else if (m == "poisson") metrics_.push_back({kEvPoisson, "poisson"});
     else if (m == "gamma") metrics_.push_back({kEvGamma, "gamma"});
     else if (m == "tweedie") metrics_.push_back({kEvTweedie, "tweedie"});
+    else if (m == "l1" || m == "mae" || m == "mean_absolute_error" || m == "regression_l1") metrics_.push_back({kEvL1, "l1"});
+    else if (m == "quantile") metrics_.push_back({kEvQuantile, "quantile"});
+    else if (m == "mape" || m == "mean_absolute_percentage_error") metrics_.push_back({kEvMape, "mape"});
     else if (m == "multi_logloss" || m == "multiclass" || m == "softmax") metrics_.push_back({kEvMultiLogloss, "multi_logloss"});
     else if (m == "multi_error") metrics_.push_back({kEvMultiError, "multi_error"});
     else if (m == "ndcg" || m == "lambdarank" || m == "rank_xendcg" || m == "xendcg") {
@@ -174,8 +177,8 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
     LGB_CHECK(obj_ != kMulticlass, "metric=%s is not defined for objective=multiclass (multi_logloss, multi_error)", m.name.c_str());
     if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || m.kind >= kEvHuber) {
       const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError
-                       : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;
-      const double p0 = m.kind == kEvHuber ? cfg_.alpha : m.kind == kEvFair ? cfg_.fair_c : cfg_.tweedie_variance_power;
+                       : m.kind >= kEvL1 ? kMetricL1 + (m.kind - kEvL1) : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;
+      const double p0 = (m.kind == kEvHuber || m.kind == kEvQuantile) ? cfg_.alpha : m.kind == kEvFair ? cfg_.fair_c : cfg_.tweedie_variance_power;
       k_metric_point<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, kind, cfg_.sigmoid, d_mpart_.p,
                                                                     LogLink() ? 1 : 0, p0);
       k_metric_final<<<1, kMetricThreads, 0, stream_>>>(d_mpart_.p, kMetricBlocks, d_mout_.p);

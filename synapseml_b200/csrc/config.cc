@@ -146,6 +146,8 @@ void Config::Set(const std::string& params) {
   for (auto a : kL2)
     if (objective == a) objective = "regression";
   if (objective == "softmax") objective = "multiclass";
+  if (objective == "l1" || objective == "mean_absolute_error" || objective == "mae") objective = "regression_l1";
+  if (objective == "mean_absolute_percentage_error") objective = "mape";
   if (boosting == "random_forest") boosting = "rf";
   if (boosting == "gbrt") boosting = "gbdt";
 }

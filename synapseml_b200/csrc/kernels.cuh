@@ -72,13 +72,29 @@ __global__ void k_grad_l2(const double* __restrict__ score, const float* __restr
 
 // Huber / Fair / Poisson / Gamma / Tweedie (upstream regression_objective.hpp); kind = Booster::Obj.  p0: alpha | fair_c |
 // exp(poisson_max_delta_step) | - | tweedie_variance_power.
+// kinds 10 / 11 / 12: regression_l1 (sign of the error), quantile (p0 = alpha, kept as a float as upstream does), mape (sign of the
+// error times label_weight = 1 / max(1, |label|) [* weight]); unit hessians (the row weight when there are weights).
 __global__ void k_grad_point(int kind, const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
-                             float* __restrict__ grad, float* __restrict__ hess, int n, double p0) {
+                             float* __restrict__ grad, float* __restrict__ hess, int n, double p0, const float* __restrict__ label_weight) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const double sc = score[i];
     const double y = label[i];
     double g, h;
-    if (kind == 4) {            // huber
+    if (kind >= 10) {
+      const double diff = sc - y;
+      if (kind == 10) {
+        g = SignD(diff);
+      } else if (kind == 11) {
+        const float delta = static_cast<float>(diff);
+        const float alpha = static_cast<float>(p0);
+        g = delta >= 0 ? (1.0f - alpha) : -alpha;
+      } else {
+        grad[i] = static_cast<float>(SignD(diff) * label_weight[i]);      // label_weight already carries the row weight
+        hess[i] = weight == nullptr ? 1.0f : weight[i];
+        continue;
+      }
+      h = 1.0;
+    } else if (kind == 4) {            // huber
       const double diff = sc - y;
       g = fabs(diff) <= p0 ? diff : SignD(diff) * p0;
       h = 1.0;

@@ -17,7 +17,7 @@ constexpr int kMetricBlocks = 592;
 constexpr int kMetricThreads = 256;
 
 enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2, kMetricHuber = 3, kMetricFair = 4, kMetricPoisson = 5,
-                   kMetricGamma = 6, kMetricTweedie = 7 };
+                   kMetricGamma = 6, kMetricTweedie = 7, kMetricL1 = 8, kMetricQuantile = 9, kMetricMape = 10 };
 
 __device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -62,6 +62,13 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
         const double b = -((-theta) > 0.0 ? log(-theta) : -INFINITY);
         const double c = (lab > 0.0 ? log(lab) : -INFINITY) - (lab > 0.0 ? log(lab) : -INFINITY);
         loss = -((lab * theta - b) + c);
+      } else if (kind == kMetricL1) {
+        loss = fabs(t - lab);
+      } else if (kind == kMetricQuantile) {       // p0 = alpha
+        const double delta = lab - t;
+        loss = delta < 0 ? (p0 - 1.0f) * delta : p0 * delta;
+      } else if (kind == kMetricMape) {
+        loss = fabs(lab - t) / fmax(1.0, fabs(lab));
       } else {                                    // tweedie, p0 = rho
         const double sc = t < 1e-10 ? 1e-10 : t;
         const double a = lab * exp((1 - p0) * log(sc)) / (1 - p0);

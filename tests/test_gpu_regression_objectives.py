@@ -94,3 +94,67 @@ def test_regressor_estimator_with_tweedie(native):
     pred = model.transform(X)["prediction"]
     assert (pred > 0).all()                                           # exp link
     assert np.corrcoef(pred, y)[0, 1] > 0.5 and abs(pred.mean() - y.mean()) < 0.05 * y.mean()
+
+
+# ---- l1 / quantile / mape: the objectives whose leaf outputs are re-fit as percentiles of the residuals (RenewTreeOutput)
+RENEW = {
+    "regression_l1": "objective=regression_l1",
+    "quantile": "objective=quantile alpha=0.8",
+    "mape": "objective=mape",
+}
+
+
+def skewed_targets(n):
+    X, y = S.dense100(n, f=12)
+    rng = np.random.Generator(np.random.PCG64(17))
+    y = (y + np.abs(y) * 0.4 + rng.exponential(0.5, n)).astype(np.float32)      # continuous, asymmetric: percentiles differ from means
+    return X, y
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+@pytest.mark.parametrize("name", sorted(RENEW))
+def test_percentile_objectives_quantized_models_are_byte_identical(native, oracle, name, weighted):
+    X, y = skewed_targets(30000)
+    w = np.random.Generator(np.random.PCG64(5)).uniform(0.5, 3.0, len(y)).astype(np.float32) if weighted else None
+    params = RENEW[name] + " num_leaves=31 max_bin=63 learning_rate=0.2 use_quantized_grad=true stochastic_rounding=false verbosity=-1"
+    nd, nb, ob = train_both(oracle, X, y, params, 8, weight=w)
+    ms = nb.model()
+    assert strip_parameters(ms) == strip_parameters(ob.save_model_to_string())
+    assert np.array_equal(nb.scores(), ob.scores())
+    assert ("objective=%s\n" % name) in ms
+    raw = predict(nb.handle, X[:2000], 1)
+    assert np.array_equal(raw, TextModel(ms).predict_raw(X[:2000])) and np.array_equal(predict(nb.handle, X[:2000], 0), raw)
+    nb.free()
+    nd.free()
+
+
+def test_quantile_regressor_covers_alpha_of_the_labels_and_reports_its_metric(native):
+    X, y = skewed_targets(60000)
+    model_hi = LightGBMRegressor(objective="quantile", alpha=0.9, numIterations=60, numLeaves=31, learningRate=0.2).fit(LocalDataFrame.from_arrays(X, y))
+    model_lo = LightGBMRegressor(objective="quantile", alpha=0.1, numIterations=60, numLeaves=31, learningRate=0.2).fit(LocalDataFrame.from_arrays(X, y))
+    hi, lo = model_hi.transform(X)["prediction"], model_lo.transform(X)["prediction"]
+    assert abs((y <= hi).mean() - 0.9) < 0.02 and abs((y <= lo).mean() - 0.1) < 0.02
+    # the default metric of the objective, on the training data, against numpy
+    params = "objective=quantile alpha=0.8 num_leaves=15 max_bin=63 verbosity=-1"
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    for _ in range(5):
+        nb.update()
+    n, out = C.c_int(), np.zeros(4)
+    validate(lightgbmlib().LGBM_BoosterGetEval(nb.handle, 0, C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+    d = y.astype(np.float64) - nb.scores()
+    assert n.value == 1 and np.isclose(out[0], np.where(d < 0, (np.float32(0.8) - 1.0) * d, 0.8 * d).mean(), rtol=1e-6)
+    nb.free()
+    nd.free()
+
+
+def test_l1_float_mode_first_trees_and_scores(native, oracle):
+    X, y = skewed_targets(40000)
+    params = "objective=regression_l1 num_leaves=31 max_bin=255 learning_rate=0.2 verbosity=-1"
+    nd, nb, ob = train_both(oracle, X, y, params, 8)
+    sn, so = TextModel(nb.model()).structure(), TextModel(ob.save_model_to_string()).structure()
+    assert sn[:3] == so[:3]
+    a, b = nb.scores(), ob.scores()
+    assert np.abs(a - b).max() <= FLOAT_RTOL * np.abs(b).max()
+    nb.free()
+    nd.free()

@@ -227,7 +227,7 @@ def test_both_split_search_forms_give_the_same_model(native, monkeypatch, mode):
 
 
 @pytest.mark.parametrize("mode", ["quantized", "float"])
-def test_zero_as_missing(native, oracle, mode):
+def test_zero_as_missing(native, oracle, mode, monkeypatch):
     """zeroAsMissing (LightGBMParams.scala:176): zeros and NaNs are the missing value; the split search leaves the zero bin out of
     both scans (SKIP_DEFAULT_BIN), rows of that bin follow default_left in the partition, the score pass and the predictor."""
     rng = np.random.Generator(np.random.PCG64(11))
@@ -255,4 +255,11 @@ def test_zero_as_missing(native, oracle, mode):
     assert any(((t.decision_type >> 2) & 3 == 1).any() for t in m.trees if t.num_leaves > 1)      # Zero-typed splits were exercised
     assert np.allclose(m.predict_raw(X), nb.scores(), rtol=0, atol=1e-12)                          # bins and raw values route alike
     nb.free()
+    # the warp form of the split search skips the zero bin in the same way
+    monkeypatch.setenv("LGB_B200_FIND_WARP", "1")
+    nw = NativeBooster(nd, params)
+    for _ in range(10):
+        nw.update()
+    assert strip_parameters(nw.model()) == strip_parameters(ms)
+    nw.free()
     nd.free()
