@@ -7,6 +7,7 @@
 // with the column-major non-zero sample built by dataset/SampledData.scala:26-96.
 #pragma once
 #include <algorithm>
+#include <unordered_map>
 
 #include "orc_common.h"
 
@@ -121,8 +122,21 @@ struct BinMapper {
   double min_val = 0.0, max_val = 0.0;
   uint32_t default_bin = 0;
   uint32_t most_freq_bin = 0;
+  // categorical features (BinType::CategoricalBin): bin 0 collects NaN, negative, rare and unseen categories; the kept categories
+  // follow by falling sample count
+  bool categorical = false;
+  std::vector<int> bin_2_categorical;
+  std::unordered_map<int, unsigned int> categorical_2_bin;
 
   uint32_t ValueToBin(double value) const {
+    if (categorical) {
+      if (std::isnan(value)) return 0;
+      if (!(value < 2147483648.0)) return 0;      // beyond int: the cast upstream makes is undefined there; treated as unseen
+      const int iv = static_cast<int>(value);
+      if (iv < 0) return 0;
+      auto it = categorical_2_bin.find(iv);
+      return it == categorical_2_bin.end() ? 0 : it->second;
+    }
     if (std::isnan(value)) {
       if (missing_type == MISSING_NAN) return num_bin - 1;
       value = 0.0;
@@ -138,7 +152,8 @@ struct BinMapper {
 
   // values: the sampled NON-ZERO values of the feature (copied by the caller; sorted in place here).
   void FindBin(double* values, int num_sample_values, size_t total_sample_cnt, int max_bin, int min_data_in_bin,
-               int min_split_data, bool pre_filter, bool use_missing, bool zero_as_missing) {
+               int min_split_data, bool pre_filter, bool use_missing, bool zero_as_missing, bool is_categorical = false) {
+    categorical = is_categorical;
     int na_cnt = 0;
     int tmp = 0;
     for (int i = 0; i < num_sample_values; ++i) {
@@ -182,7 +197,51 @@ struct BinMapper {
     min_val = distinct.front();
     max_val = distinct.back();
     int nd = static_cast<int>(distinct.size());
-    if (missing_type == MISSING_ZERO) {
+    std::vector<int> cnt_in_bin;
+    if (categorical) {
+      // BinMapper::FindBin, bin_type == CategoricalBin: values become ints (negative ones count as missing), the categories are
+      // taken by falling count until 99 % of the sample is covered AND max_bin bins exist; categories seen fewer than
+      // min_data_in_bin times end the list (except the first two)
+      std::vector<int> dvi, cti;
+      for (int i = 0; i < nd; ++i) {
+        const int val = distinct[i] < 2147483648.0 ? static_cast<int>(distinct[i]) : -1;      // beyond int: counted as missing
+        if (val < 0) na_cnt += counts[i];
+        else if (dvi.empty() || val != dvi.back()) { dvi.push_back(val); cti.push_back(counts[i]); }
+        else cti.back() += counts[i];
+      }
+      num_bin = 0;
+      const int rest_cnt = static_cast<int>(total_sample_cnt - na_cnt);
+      if (rest_cnt > 0) {
+        std::vector<int> order(dvi.size());
+        for (size_t i = 0; i < order.size(); ++i) order[i] = static_cast<int>(i);
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cti[a] > cti[b]; });     // SortForPair(..., is_reverse)
+        const int cut_cnt = RoundInt((total_sample_cnt - na_cnt) * 0.99f);
+        size_t cur_cat = 0;
+        int used_cnt = 0;
+        int distinct_cnt = static_cast<int>(dvi.size());
+        if (na_cnt > 0) ++distinct_cnt;
+        max_bin = std::min(distinct_cnt, max_bin);
+        bin_2_categorical.assign(1, -1);
+        categorical_2_bin.clear();
+        categorical_2_bin[-1] = 0;
+        cnt_in_bin.assign(1, 0);
+        num_bin = 1;
+        while (cur_cat < order.size() && (used_cnt < cut_cnt || num_bin < max_bin)) {
+          const int o = order[cur_cat];
+          if (cti[o] < min_data_in_bin && cur_cat > 1) break;
+          bin_2_categorical.push_back(dvi[o]);
+          categorical_2_bin[dvi[o]] = static_cast<unsigned int>(num_bin);
+          used_cnt += cti[o];
+          cnt_in_bin.push_back(cti[o]);
+          ++num_bin;
+          ++cur_cat;
+        }
+        // MissingType::None here says that every category seen has a bin of its own
+        missing_type = (cur_cat == order.size() && na_cnt == 0) ? MISSING_NONE : MISSING_NAN;
+        cnt_in_bin[0] = static_cast<int>(total_sample_cnt - used_cnt);
+      }
+      bin_upper_bound.clear();
+    } else if (missing_type == MISSING_ZERO) {
       bin_upper_bound = FindBinWithZeroAsOneBin(distinct.data(), counts.data(), nd, max_bin, total_sample_cnt, min_data_in_bin);
       if (bin_upper_bound.size() == 2) missing_type = MISSING_NONE;
     } else if (missing_type == MISSING_NONE) {
@@ -191,9 +250,9 @@ struct BinMapper {
       bin_upper_bound = FindBinWithZeroAsOneBin(distinct.data(), counts.data(), nd, max_bin - 1, total_sample_cnt - na_cnt, min_data_in_bin);
       bin_upper_bound.push_back(std::numeric_limits<double>::quiet_NaN());
     }
-    num_bin = static_cast<int>(bin_upper_bound.size());
-    std::vector<int> cnt_in_bin(num_bin, 0);
-    {
+    if (!categorical) {
+      num_bin = static_cast<int>(bin_upper_bound.size());
+      cnt_in_bin.assign(num_bin, 0);
       int i_bin = 0;
       for (int i = 0; i < nd; ++i) {
         while (distinct[i] > bin_upper_bound[i_bin] && i_bin < num_bin - 1) ++i_bin;
@@ -203,13 +262,23 @@ struct BinMapper {
     }
     is_trivial = num_bin <= 1;
     if (!is_trivial && pre_filter) {
-      // NeedFilter: no cut leaves >= min_split_data samples on both sides
+      // NeedFilter: no cut leaves >= min_split_data samples on both sides (categorical: no single bin against the rest, looked at
+      // only when there are at most two bins)
       bool need = true;
       int sum_left = 0;
       int total = static_cast<int>(total_sample_cnt);
-      for (size_t i = 0; i + 1 < cnt_in_bin.size(); ++i) {
-        sum_left += cnt_in_bin[i];
-        if (sum_left >= min_split_data && total - sum_left >= min_split_data) { need = false; break; }
+      if (!categorical) {
+        for (size_t i = 0; i + 1 < cnt_in_bin.size(); ++i) {
+          sum_left += cnt_in_bin[i];
+          if (sum_left >= min_split_data && total - sum_left >= min_split_data) { need = false; break; }
+        }
+      } else if (cnt_in_bin.size() <= 2) {
+        for (size_t i = 0; i + 1 < cnt_in_bin.size(); ++i) {
+          sum_left = cnt_in_bin[i];
+          if (sum_left >= min_split_data && total - sum_left >= min_split_data) { need = false; break; }
+        }
+      } else {
+        need = false;
       }
       if (need) is_trivial = true;
     }

@@ -94,7 +94,7 @@ int ORC_DatasetGetFeatureInfo(void* h, int real_feature, int* num_bin, int* miss
 int ORC_DatasetGetBinUpperBounds(void* h, int real_feature, double* out) {
   ORC_BEGIN
   const BinMapper& m = static_cast<Dataset*>(h)->mappers.at(real_feature);
-  for (int i = 0; i < m.num_bin; ++i) out[i] = m.bin_upper_bound[i];
+  for (int i = 0; i < m.num_bin; ++i) out[i] = m.categorical ? static_cast<double>(m.bin_2_categorical[i]) : m.bin_upper_bound[i];   // categorical: the category of every bin
   ORC_END
 }
 

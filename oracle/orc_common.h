@@ -195,6 +195,10 @@ struct Config {
   bool lambdarank_norm = true;
   std::vector<double> label_gain;
   std::vector<int> eval_at;
+  // categorical features (upstream config.h defaults): column indexes, and the knobs of the categorical split search
+  std::vector<int> categorical_feature;
+  int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
+  double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // everything seen, canonical key -> value (first writer wins)
 
   static std::string Canon(const std::string& k) {
@@ -227,6 +231,8 @@ struct Config {
         {"num_machine", "num_machines"},
         {"verbose", "verbosity"},
         {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"},
+        {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"}, {"cat_column", "categorical_feature"},
+        {"categorical_features", "categorical_feature"},
     };
     auto it = alias.find(k);
     return it == alias.end() ? k : it->second;
@@ -327,6 +333,9 @@ struct Config {
     getb("lambdarank_norm", &lambdarank_norm);
     if (has("label_gain")) label_gain = ParseList<double>(kv["label_gain"]);
     if (has("eval_at")) eval_at = ParseList<int>(kv["eval_at"]);
+    if (has("categorical_feature")) categorical_feature = ParseList<int>(kv["categorical_feature"]);
+    geti("max_cat_to_onehot", &max_cat_to_onehot); geti("max_cat_threshold", &max_cat_threshold); geti("min_data_per_group", &min_data_per_group);
+    getd("cat_smooth", &cat_smooth); getd("cat_l2", &cat_l2);
     // objective aliases
     if (objective == "regression_l2" || objective == "l2" || objective == "mean_squared_error" || objective == "mse" ||
         objective == "l2_root" || objective == "root_mean_squared_error" || objective == "rmse")

@@ -31,6 +31,8 @@ struct SplitInfo {
   double left_sum_gradient = 0.0, left_sum_hessian = 0.0, right_sum_gradient = 0.0, right_sum_hessian = 0.0;
   int64_t left_int_g = 0, left_int_h = 0, right_int_g = 0, right_int_h = 0;
   bool default_left = true;
+  std::vector<uint32_t> cat_threshold;      // categorical split: the bins that go left (num_cat_threshold = its size), else empty
+  bool categorical = false;
   void Reset() { *this = SplitInfo(); }
   // upstream SplitInfo::operator> : larger gain wins; equal gain -> smaller feature index (-1 counts as +inf)
   bool BetterThan(const SplitInfo& o) const {
@@ -44,6 +46,9 @@ struct SplitInfo {
 struct SplitParams {
   double l1, l2, max_delta_step, min_gain_to_split, min_sum_hessian;
   int min_data_in_leaf;
+  // categorical split search
+  int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
+  double cat_smooth = 10.0, cat_l2 = 10.0;
 };
 
 inline double ThresholdL1(double s, double l1) {
@@ -251,6 +256,143 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
   return splittable;
 }
 
+// Categorical split search (FindBestThresholdCategoricalInner / ...IntInner).  Bin 0 (NaN, negative, rare and unseen categories) is
+// never a candidate and always goes right.  Few bins (num_bin <= max_cat_to_onehot): every category alone against the rest.
+// Otherwise the bins with at least cat_smooth rows are sorted by sum_gradient / (sum_hessian + cat_smooth) and prefixes of that
+// order are tried from both ends (at most max_cat_threshold categories, groups of at least min_data_per_group rows), with cat_l2
+// added to lambda_l2.  QUANT: hist holds integers and every sum is int_sum * scale, without the kEpsilon terms of the float form.
+template <bool QUANT, typename HistT>
+inline bool FindBestThresholdCategorical(const HistT* hist, const BinMapper& m, double leaf_sum_g, double leaf_sum_h, int64_t int_sum_g,
+                                         int64_t int_sum_h, double grad_scale, double hess_scale, data_size_t num_data,
+                                         const SplitParams& p_in, SplitInfo* out) {
+  out->default_left = false;
+  out->gain = kMinScore;
+  out->categorical = true;
+  SplitParams p = p_in;
+  double sum_gradient, sum_hessian, cnt_factor;
+  if (QUANT) {
+    if (int_sum_h <= 0) return false;
+    sum_gradient = static_cast<double>(int_sum_g) * grad_scale;
+    sum_hessian = static_cast<double>(int_sum_h) * hess_scale;
+    cnt_factor = static_cast<double>(num_data) / static_cast<double>(int_sum_h);
+  } else {
+    sum_gradient = leaf_sum_g;
+    sum_hessian = leaf_sum_h + 2 * kEpsilon;
+    cnt_factor = num_data / sum_hessian;
+  }
+  const double eps = QUANT ? 0.0 : kEpsilon;
+  const double gain_shift = LeafGain(sum_gradient, sum_hessian, p);
+  const double min_gain_shift = gain_shift + p.min_gain_to_split;
+  const int num_bin = m.num_bin;
+  auto grad_of = [&](int b) { return QUANT ? static_cast<double>(hist[2 * b]) * grad_scale : static_cast<double>(hist[2 * b]); };
+  auto hess_of = [&](int b) { return QUANT ? static_cast<double>(hist[2 * b + 1]) * hess_scale : static_cast<double>(hist[2 * b + 1]); };
+  auto cnt_of = [&](int b) { return QUANT ? RoundInt(static_cast<double>(hist[2 * b + 1]) * cnt_factor) : RoundInt(hess_of(b) * cnt_factor); };
+  bool splittable = false;
+  double best_gain = kMinScore;
+  data_size_t best_left_count = 0;
+  double best_lg = 0, best_lh = 0;
+  int64_t best_int_lg = 0, best_int_lh = 0;
+  int best_threshold = -1, best_dir = 1;
+  const bool use_onehot = num_bin <= p.max_cat_to_onehot;
+  std::vector<int> sorted_idx;
+  int used_bin = -1;
+  if (use_onehot) {
+    for (int t = 1; t < num_bin; ++t) {
+      const double grad = grad_of(t), hess = hess_of(t);
+      const data_size_t cnt = cnt_of(t);
+      if (cnt < p.min_data_in_leaf || hess < p.min_sum_hessian) continue;
+      const data_size_t other_count = num_data - cnt;
+      if (other_count < p.min_data_in_leaf) continue;
+      const double sum_other_hessian = QUANT ? static_cast<double>(int_sum_h - static_cast<int64_t>(hist[2 * t + 1])) * hess_scale
+                                             : sum_hessian - hess - kEpsilon;
+      if (sum_other_hessian < p.min_sum_hessian) continue;
+      const double sum_other_gradient = QUANT ? static_cast<double>(int_sum_g - static_cast<int64_t>(hist[2 * t])) * grad_scale
+                                              : sum_gradient - grad;
+      const double gain = SplitGain(sum_other_gradient, sum_other_hessian, grad, hess + eps, p);
+      if (gain <= min_gain_shift) continue;
+      splittable = true;
+      if (gain > best_gain) {
+        best_threshold = t; best_lg = grad; best_lh = hess + eps; best_left_count = cnt; best_gain = gain;
+        if (QUANT) { best_int_lg = static_cast<int64_t>(hist[2 * t]); best_int_lh = static_cast<int64_t>(hist[2 * t + 1]); }
+      }
+    }
+  } else {
+    for (int i = 1; i < num_bin; ++i)
+      if (cnt_of(i) >= p.cat_smooth) sorted_idx.push_back(i);
+    used_bin = static_cast<int>(sorted_idx.size());
+    p.l2 += p.cat_l2;
+    auto ctr = [&](int b) { return grad_of(b) / (hess_of(b) + p.cat_smooth); };
+    std::stable_sort(sorted_idx.begin(), sorted_idx.end(), [&](int i, int j) { return ctr(i) < ctr(j); });
+    const int max_num_cat = std::min(p.max_cat_threshold, (used_bin + 1) / 2);
+    for (int pass = 0; pass < 2; ++pass) {
+      const int dir = pass == 0 ? 1 : -1;
+      int start_pos = pass == 0 ? 0 : used_bin - 1;
+      data_size_t cnt_cur_group = 0, left_count = 0;
+      double sum_left_gradient = 0.0, sum_left_hessian = kEpsilon;
+      int64_t int_lg = 0, int_lh = 0;
+      for (int i = 0; i < used_bin && i < max_num_cat; ++i) {
+        const int t = sorted_idx[start_pos];
+        start_pos += dir;
+        const data_size_t cnt = cnt_of(t);
+        if (QUANT) {
+          int_lg += static_cast<int64_t>(hist[2 * t]); int_lh += static_cast<int64_t>(hist[2 * t + 1]);
+          sum_left_gradient = static_cast<double>(int_lg) * grad_scale;
+          sum_left_hessian = static_cast<double>(int_lh) * hess_scale;
+        } else {
+          sum_left_gradient += grad_of(t);
+          sum_left_hessian += hess_of(t);
+        }
+        left_count += cnt;
+        cnt_cur_group += cnt;
+        if (left_count < p.min_data_in_leaf || sum_left_hessian < p.min_sum_hessian) continue;
+        const data_size_t right_count = num_data - left_count;
+        if (right_count < p.min_data_in_leaf || right_count < p.min_data_per_group) break;
+        const double sum_right_hessian = QUANT ? static_cast<double>(int_sum_h - int_lh) * hess_scale : sum_hessian - sum_left_hessian;
+        if (sum_right_hessian < p.min_sum_hessian) break;
+        if (cnt_cur_group < p.min_data_per_group) continue;
+        cnt_cur_group = 0;
+        const double sum_right_gradient = QUANT ? static_cast<double>(int_sum_g - int_lg) * grad_scale : sum_gradient - sum_left_gradient;
+        const double gain = SplitGain(sum_left_gradient, sum_left_hessian, sum_right_gradient, sum_right_hessian, p);
+        if (gain <= min_gain_shift) continue;
+        splittable = true;
+        if (gain > best_gain) {
+          best_left_count = left_count; best_lg = sum_left_gradient; best_lh = sum_left_hessian;
+          best_int_lg = int_lg; best_int_lh = int_lh;
+          best_threshold = i; best_gain = gain; best_dir = dir;
+        }
+      }
+    }
+  }
+  if (splittable) {
+    out->left_count = best_left_count;
+    out->right_count = num_data - best_left_count;
+    if (QUANT) {
+      const int64_t rg = int_sum_g - best_int_lg, rh = int_sum_h - best_int_lh;
+      const double brg = static_cast<double>(rg) * grad_scale, brh = static_cast<double>(rh) * hess_scale;
+      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_sum_gradient = best_lg; out->left_sum_hessian = best_lh;
+      out->left_int_g = best_int_lg; out->left_int_h = best_int_lh;
+      out->right_output = LeafOutput(brg, brh, p);
+      out->right_sum_gradient = brg; out->right_sum_hessian = brh;
+      out->right_int_g = rg; out->right_int_h = rh;
+    } else {
+      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_sum_gradient = best_lg; out->left_sum_hessian = best_lh - kEpsilon;
+      out->right_output = LeafOutput(sum_gradient - best_lg, sum_hessian - best_lh, p);
+      out->right_sum_gradient = sum_gradient - best_lg; out->right_sum_hessian = sum_hessian - best_lh - kEpsilon;
+    }
+    out->gain = best_gain - min_gain_shift;
+    if (use_onehot) {
+      out->cat_threshold.assign(1, static_cast<uint32_t>(best_threshold));
+    } else {
+      out->cat_threshold.resize(best_threshold + 1);
+      for (int i = 0; i <= best_threshold; ++i)
+        out->cat_threshold[i] = static_cast<uint32_t>(best_dir == 1 ? sorted_idx[i] : sorted_idx[used_bin - 1 - i]);
+    }
+  }
+  return splittable;
+}
+
 // PercentileFun / WeightedPercentileFun (upstream src/objective/regression_objective.hpp), on a copy of the data.  alpha_f: the
 // quantile objective keeps alpha as a float, so (1.0f - alpha) * cnt is float arithmetic there; L1 uses the double 0.5.
 template <typename T>
@@ -374,7 +516,8 @@ class Booster {
     }
     total_rows = off;
     has_weights = ds[0]->has_weight;
-    sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf};
+    sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf,
+          cfg.max_cat_to_onehot, cfg.max_cat_threshold, cfg.min_data_per_group, cfg.cat_smooth, cfg.cat_l2};
     if (cfg.boosting == "gbdt") boost = BOOST_GBDT;
     else if (cfg.boosting == "rf") boost = BOOST_RF;
     else if (cfg.boosting == "dart") boost = BOOST_DART;
@@ -1026,7 +1169,14 @@ class Booster {
       const BinMapper& m = shards[0].ds->inner_mapper(f);
       SplitInfo si;
       bool ok;
-      if (cfg.use_quantized_grad) {
+      if (m.categorical) {
+        if (cfg.use_quantized_grad)
+          ok = FindBestThresholdCategorical<true>(hist_i[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, L.int_g, L.int_h,
+                                                  grad_scale, hess_scale, L.count, sp, &si);
+        else
+          ok = FindBestThresholdCategorical<false>(hist_f[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, 0, 0, 1.0, 1.0,
+                                                   L.count, sp, &si);
+      } else if (cfg.use_quantized_grad) {
         ok = FindBestThresholdInt(hist_i[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.int_g, L.int_h, grad_scale,
                                   hess_scale, L.count, sp, &si);
       } else {
@@ -1142,7 +1292,8 @@ class Booster {
         const data_size_t r = sh.indices[b + i];
         const uint32_t bin = d->bin_at(bs.feature, r);
         bool go_left;
-        if ((m.missing_type == MISSING_NAN && bin == nan_bin) || (m.missing_type == MISSING_ZERO && bin == m.default_bin)) go_left = bs.default_left;
+        if (bs.categorical) go_left = std::find(bs.cat_threshold.begin(), bs.cat_threshold.end(), bin) != bs.cat_threshold.end();
+        else if ((m.missing_type == MISSING_NAN && bin == nan_bin) || (m.missing_type == MISSING_ZERO && bin == m.default_bin)) go_left = bs.default_left;
         else go_left = bin <= bs.threshold;
         if (go_left) sh.tmp_left[nl++] = r; else sh.tmp_right[nr++] = r;
       }
@@ -1154,9 +1305,18 @@ class Booster {
       tot_left += nl; tot_right += nr;
     }
     if (!dp) { bs.left_count = tot_left; bs.right_count = tot_right; }   // serial learner: true counts (update_cnt)
-    *right_leaf = tree->Split(best_leaf, bs.feature, bs.real_feature, bs.threshold, m.bin_upper_bound[bs.threshold],
-                              bs.left_output, bs.right_output, bs.left_count, bs.right_count, bs.left_sum_hessian,
-                              bs.right_sum_hessian, static_cast<float>(bs.gain), m.missing_type, bs.default_left);
+    if (bs.categorical) {      // SerialTreeLearner::SplitInner: one bitset over the bins, one over the category values
+      std::vector<int> bins(bs.cat_threshold.begin(), bs.cat_threshold.end()), cats;
+      for (int b : bins) cats.push_back(m.bin_2_categorical[b]);
+      *right_leaf = tree->SplitCategorical(best_leaf, bs.feature, bs.real_feature, Tree::ConstructBitset(bins.data(), static_cast<int>(bins.size())),
+                                           Tree::ConstructBitset(cats.data(), static_cast<int>(cats.size())), bs.left_output, bs.right_output,
+                                           bs.left_count, bs.right_count, bs.left_sum_hessian, bs.right_sum_hessian,
+                                           static_cast<float>(bs.gain), m.missing_type);
+    } else {
+      *right_leaf = tree->Split(best_leaf, bs.feature, bs.real_feature, bs.threshold, m.bin_upper_bound[bs.threshold],
+                                bs.left_output, bs.right_output, bs.left_count, bs.right_count, bs.left_sum_hessian,
+                                bs.right_sum_hessian, static_cast<float>(bs.gain), m.missing_type, bs.default_left);
+    }
     std::vector<char> parent_spl = leaves[best_leaf].splittable;
     Leaf& L = leaves[*left_leaf];
     Leaf& R = leaves[*right_leaf];
@@ -1338,7 +1498,11 @@ class Booster {
       const int mt = (t.decision_type[node] >> 2) & 3;
       const bool dl = (t.decision_type[node] & 2) != 0;
       bool left;
-      if ((mt == MISSING_NAN && bin == static_cast<uint32_t>(m.num_bin - 1)) || (mt == MISSING_ZERO && bin == m.default_bin)) left = dl;
+      if (t.decision_type[node] & 1) {
+        const int k = static_cast<int>(t.threshold_in_bin[node]);
+        left = Tree::FindInBitset(t.cat_threshold_inner.data() + t.cat_boundaries_inner[k], t.cat_boundaries_inner[k + 1] - t.cat_boundaries_inner[k],
+                                  static_cast<int>(bin));
+      } else if ((mt == MISSING_NAN && bin == static_cast<uint32_t>(m.num_bin - 1)) || (mt == MISSING_ZERO && bin == m.default_bin)) left = dl;
       else left = bin <= t.threshold_in_bin[node];
       node = left ? t.left_child[node] : t.right_child[node];
     }
@@ -1372,7 +1536,9 @@ class Booster {
     for (int j = 0; j < d->num_total_features; ++j) {
       if (j) s += ' ';
       const BinMapper& m = d->mappers[j];
-      if (m.is_trivial) s += "none"; else s += "[" + FmtG17(m.min_val) + ":" + FmtG17(m.max_val) + "]";
+      if (m.is_trivial) s += "none";
+      else if (m.categorical) { for (size_t b = 0; b < m.bin_2_categorical.size(); ++b) { if (b) s += ':'; s += std::to_string(m.bin_2_categorical[b]); } }   // BinMapper::bin_info_string
+      else s += "[" + FmtG17(m.min_val) + ":" + FmtG17(m.max_val) + "]";
     }
     s += "\n";
     std::vector<std::string> blocks;

@@ -1,7 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h header; parity unpinned).
 //
-// Tree container and LightGBM text-model block.  Restates upstream Tree::Split / Shrinkage / AddBias / ToString
-// (src/io/tree.cpp, include/LightGBM/tree.h) and Tree::Decision for numerical splits, SURVEY.md A.8/A.10.
+// Tree container and LightGBM text-model block.  Restates upstream Tree::Split / SplitCategorical / Shrinkage / AddBias / ToString
+// (src/io/tree.cpp, include/LightGBM/tree.h) and Tree::NumericalDecision / CategoricalDecision, SURVEY.md A.8/A.10.
 // Reference consumer: LGBM_BoosterSaveModelToStringSWIG at lightgbm/.../booster/LightGBMBooster.scala:272-278.
 #pragma once
 #include <cstdio>
@@ -26,6 +26,26 @@ struct Tree {
   std::vector<double> leaf_value, leaf_weight, internal_value, internal_weight;
   std::vector<int> leaf_count, internal_count;
   double shrinkage = 1.0;
+  // categorical splits: node i of that kind stores its index among them in threshold[i]; its categories are the bits set in words
+  // [cat_boundaries[k], cat_boundaries[k + 1]) of cat_threshold (category values) / ..._inner (bins)
+  int num_cat = 0;
+  std::vector<int> cat_boundaries{0}, cat_boundaries_inner{0};
+  std::vector<uint32_t> cat_threshold, cat_threshold_inner;
+
+  static bool FindInBitset(const uint32_t* bits, int n, int pos) {
+    const int i1 = pos / 32;
+    if (i1 >= n) return false;
+    return (bits[i1] >> (pos % 32)) & 1;
+  }
+  static std::vector<uint32_t> ConstructBitset(const int* vals, int n) {
+    std::vector<uint32_t> ret;
+    for (int i = 0; i < n; ++i) {
+      const int i1 = vals[i] / 32, i2 = vals[i] % 32;
+      if (static_cast<int>(ret.size()) < i1 + 1) ret.resize(i1 + 1, 0);
+      ret[i1] |= (1u << i2);
+    }
+    return ret;
+  }
 
   explicit Tree(int max_leaves_) : max_leaves(max_leaves_) {
     int n = std::max(max_leaves, 2);
@@ -74,6 +94,24 @@ struct Tree {
     return num_leaves - 1;
   }
 
+  // Tree::SplitCategorical: bitsets over bins (threshold_bin) and over category values (threshold_cat); default_left is false
+  int SplitCategorical(int leaf, int feature_inner, int real_feature, const std::vector<uint32_t>& threshold_bin,
+                       const std::vector<uint32_t>& threshold_cat, double left_value, double right_value, int left_cnt, int right_cnt,
+                       double left_weight, double right_weight, float gain, int missing_type) {
+    const int new_node = num_leaves - 1;
+    Split(leaf, feature_inner, real_feature, 0, 0.0, left_value, right_value, left_cnt, right_cnt, left_weight, right_weight, gain,
+          missing_type, false);
+    decision_type[new_node] = static_cast<int8_t>(1 | ((missing_type & 3) << 2));
+    threshold_in_bin[new_node] = static_cast<uint32_t>(num_cat);
+    threshold[new_node] = num_cat;
+    ++num_cat;
+    cat_boundaries.push_back(cat_boundaries.back() + static_cast<int>(threshold_cat.size()));
+    cat_threshold.insert(cat_threshold.end(), threshold_cat.begin(), threshold_cat.end());
+    cat_boundaries_inner.push_back(cat_boundaries_inner.back() + static_cast<int>(threshold_bin.size()));
+    cat_threshold_inner.insert(cat_threshold_inner.end(), threshold_bin.begin(), threshold_bin.end());
+    return num_leaves - 1;
+  }
+
   void Shrinkage(double rate) {
     for (int i = 0; i < num_leaves - 1; ++i) {
       leaf_value[i] = MaybeRoundToZero(leaf_value[i] * rate);
@@ -101,6 +139,16 @@ struct Tree {
       double fval = row[split_feature[node]];
       int mt = (decision_type[node] >> 2) & 3;
       bool dl = (decision_type[node] & 2) != 0;
+      if (decision_type[node] & 1) {      // CategoricalDecision: NaN, negative and unlisted values go right
+        bool left = false;
+        if (!std::isnan(fval) && fval < 2147483648.0) {
+          const int iv = static_cast<int>(fval);
+          const int k = static_cast<int>(threshold[node]);
+          left = iv >= 0 && FindInBitset(cat_threshold.data() + cat_boundaries[k], cat_boundaries[k + 1] - cat_boundaries[k], iv);
+        }
+        node = left ? left_child[node] : right_child[node];
+        continue;
+      }
       if (std::isnan(fval) && mt != MISSING_NAN) fval = 0.0;
       if ((mt == MISSING_ZERO && fval >= -kZeroThreshold && fval <= kZeroThreshold) || (mt == MISSING_NAN && std::isnan(fval))) {
         node = dl ? left_child[node] : right_child[node];
@@ -125,10 +173,9 @@ struct Tree {
     auto f17 = [](double v) { return FmtG17(v); };
     auto fg = [](float v) { return FmtG(v); };
     auto fd = [](int8_t v) { return std::to_string(static_cast<int>(v)); };
-    (void)fu;
     std::string s;
     s += "num_leaves=" + std::to_string(num_leaves) + "\n";
-    s += "num_cat=0\n";
+    s += "num_cat=" + std::to_string(num_cat) + "\n";
     if (num_leaves > 1) {
       int ni = num_leaves - 1;
       s += "split_feature=" + Join(split_feature, ni, fi) + "\n";
@@ -143,6 +190,10 @@ struct Tree {
       s += "internal_value=" + Join(internal_value, ni, f17) + "\n";
       s += "internal_weight=" + Join(internal_weight, ni, f17) + "\n";
       s += "internal_count=" + Join(internal_count, ni, fi) + "\n";
+      if (num_cat > 0) {
+        s += "cat_boundaries=" + Join(cat_boundaries, num_cat + 1, fi) + "\n";
+        s += "cat_threshold=" + Join(cat_threshold, static_cast<int>(cat_threshold.size()), fu) + "\n";
+      }
     } else {
       s += "leaf_value=" + FmtG17(leaf_value[0]) + "\n";
     }

@@ -79,6 +79,8 @@ struct BatchItem {
   int est_left, est_right;                      // the split's count estimates (the data-parallel learner's global counts)
   long long left_int_g, left_int_h, right_int_g, right_int_h;
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
+  int is_cat, pad_;                             // categorical split: rows whose bin has its bit set in cat_bits go left
+  unsigned int cat_bits[8];
 };
 
 struct BatchCtrl {
@@ -640,8 +642,12 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   if (!used || (!sampled && !root)) {
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
-    BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
-                         fb + f, spl, &tg, &th, sub);
+    if (fm.bin_type != 0)
+      BlockFindBestCat<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                              fb + f, spl, &tg, &th, sub);
+    else
+      BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                           fb + f, spl, &tg, &th, sub);
     if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
   }
   if (P.reduce_in_select && !sliced) {
@@ -787,7 +793,7 @@ __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, l
     while (k + 1 < bn && tile >= s_tiles[k + 1]) ++k;
     const BatchItem& it = ctrl->batch[k];
     const int n = it.src_count, begin = it.src_begin, buf = it.src_buf;
-    const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left;
+    const int thr = it.threshold, nan_bin = it.nan_bin, dl = it.default_left, is_cat = it.is_cat;
     const uint8_t* col = cm + static_cast<size_t>(it.feature) * n_pad;
     const int* idx = buf < 0 ? nullptr : (buf == 0 ? idx0r : idx1r);
     const unsigned int* bag = buf < 0 ? ctrl->bag_bits : nullptr;
@@ -821,7 +827,8 @@ __device__ __forceinline__ void PartitionTiles(const uint8_t* __restrict__ cm, l
     #pragma unroll
     for (int u = 0; u < WPW; ++u) {
       const bool valid = ent[u].x >= 0;
-      const bool left = valid && ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr));
+      const bool left = valid && (is_cat ? ((it.cat_bits[bins[u] >> 5] >> (bins[u] & 31)) & 1u) != 0u
+                                         : ((bins[u] == nan_bin) ? (dl != 0) : (bins[u] <= thr)));
       lmask[u] = __ballot_sync(0xffffffffu, left);
       rmask[u] = __ballot_sync(0xffffffffu, valid && !left);
       wl += __popc(lmask[u]); wr += __popc(rmask[u]);
@@ -1058,7 +1065,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       S.p_lw[i] = N.best.left_sum_h; S.p_rw[i] = N.best.right_sum_h;
       S.p_lc[i] = N.child_count[0]; S.p_rc[i] = N.child_count[1];
       S.p_feature[i] = N.best.feature; S.p_threshold[i] = N.best.threshold;
-      S.p_flags[i] = (N.best.default_left ? 2 : 0) | ((N.best.missing_type & 3) << 2);      // = Tree's decision_type
+      S.p_flags[i] = (N.best.is_cat ? 1 : 0) | (N.best.default_left ? 2 : 0) | ((N.best.missing_type & 3) << 2);      // = Tree's decision_type
       S.p_gain[i] = static_cast<float>(N.best.gain);
     }
     const int par = first ? pre_par : T.leaf_parent[i];
@@ -1120,6 +1127,11 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     T.internal_count[new_node] = S.p_lc[best_leaf] + S.p_rc[best_leaf];
     T.decision_type[new_node] = static_cast<signed char>(S.p_flags[best_leaf]);
     T.threshold_in_bin[new_node] = S.p_threshold[best_leaf];
+    if (T.cat_bits != nullptr) {      // a categorical node's bins that go left (all zero for a numerical node)
+      const SplitDev& cb = nodes[S.c_node[j]].best;
+      #pragma unroll
+      for (int w = 0; w < 8; ++w) T.cat_bits[new_node * 8 + w] = cb.is_cat ? cb.cat_bits[w] : 0u;
+    }
     nodes[S.c_node[j]].state = 2;
   }
   // ---- P3: order-dependent bookkeeping (reads only what P0 / P1 left in shared memory)
@@ -1185,6 +1197,9 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       it.node = nd; it.left = num_nodes + 2 * pos; it.right = it.left + 1;
       it.feature = bs.feature; it.threshold = bs.threshold; it.default_left = bs.default_left;
       it.nan_bin = bs.nan_bin;
+      it.is_cat = bs.is_cat; it.pad_ = 0;
+      #pragma unroll
+      for (int w = 0; w < 8; ++w) it.cat_bits[w] = bs.cat_bits[w];
       it.src_begin = par.begin; it.src_count = par.count; it.src_buf = par.buf;
       it.parent_slot = par.hist_slot; it.fresh_slot = num_slots + pos;
       it.child_depth = par.depth + 1;
@@ -1414,7 +1429,9 @@ constexpr int kApplyMaxFeatures = 1 << 14;      // node word: feature (14 bits) 
 // (struct ScoreMix: booster.h)
 // ctrl == nullptr: an explicit tree of nl_explicit leaves whose arrays the host uploaded (DART re-adds earlier trees); otherwise
 // the tree the learner has just finished (ctrl->done), once (ctrl->applied).
-template <int OBJ, int WPR>
+// CAT: the dataset has categorical features; a categorical node carries the marker 511 in its NaN-bin field and its decision is
+// the bin's bit in the node's cat_bits (read through the read-only cache: such nodes are few).
+template <int OBJ, int WPR, bool CAT = false>
 __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* __restrict__ rm, unsigned rm_stride,
                                                                  double* __restrict__ score, const float* __restrict__ label,
                                                                  const float* __restrict__ weight, float* __restrict__ grad,
@@ -1442,7 +1459,8 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const int dt = T.decision_type[i];
       const FeatureMetaDev fm = fmeta[f];
       // the bin whose rows follow default_left: the NaN bin, or the zero bin under zero_as_missing
-      const unsigned nan_bin = (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1)
+      const unsigned nan_bin = (CAT && (dt & 1)) ? 511u
+                               : (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1)
                                : (fm.missing_type == kMissingZero) ? static_cast<unsigned>(fm.default_bin) : 256u;
       uint2 nd;
       nd.x = static_cast<unsigned>(f) | (nan_bin << 14) | (static_cast<unsigned>(T.threshold_in_bin[i]) << 23) | ((dt & 2) ? (1u << 31) : 0u);
@@ -1473,7 +1491,8 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const int f = nd.x & 0x3fffu;
       const unsigned nan_bin = (nd.x >> 14) & 0x1ffu, thr = (nd.x >> 23) & 0xffu;
       const unsigned bin = WPR != 0 ? static_cast<unsigned>(my_bytes[f]) : static_cast<unsigned>(__ldg(rec + f));
-      const bool left = (bin == nan_bin) ? ((nd.x >> 31) != 0) : (bin <= thr);
+      bool left = (bin == nan_bin) ? ((nd.x >> 31) != 0) : (bin <= thr);
+      if (CAT && nan_bin == 511u) left = ((__ldg(T.cat_bits + node * 8 + (bin >> 5)) >> (bin & 31u)) & 1u) != 0u;
       node = left ? static_cast<int>(static_cast<short>(nd.y & 0xffffu)) : static_cast<int>(static_cast<short>(nd.y >> 16));
     } while (node >= 0);
     const double sc = (sc0 * mix.pre + s_val[~node]) * mix.post;      // (x * 1.0 + v) * 1.0 == x + v exactly

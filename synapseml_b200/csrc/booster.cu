@@ -116,6 +116,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   lp_.num_grad_quant_bins = cfg_.num_grad_quant_bins; lp_.stochastic_rounding = cfg_.stochastic_rounding;
   lp_.const_hessian = ((obj_ == kL2 || obj_ == kL1 || obj_ == kQuantile) && !has_weights_) || obj_ == kMape;      // IsConstantHessian
   lp_.seed = static_cast<unsigned int>(cfg_.seed);
+  lp_.max_cat_to_onehot = cfg_.max_cat_to_onehot; lp_.max_cat_threshold = cfg_.max_cat_threshold;
+  lp_.min_data_per_group = cfg_.min_data_per_group; lp_.cat_smooth = cfg_.cat_smooth; lp_.cat_l2 = cfg_.cat_l2;
   // 32 features or fewer: a warp of the replay kernel reduces a child's per-feature results (LGB_B200_REDUCE_IN_SELECT=0: the split
   // search's last unit does, as for wide data)
   lp_.reduce_in_select = F_ <= 32 && !(getenv("LGB_B200_REDUCE_IN_SELECT") && atoi(getenv("LGB_B200_REDUCE_IN_SELECT")) == 0);
@@ -124,6 +126,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // remote load per rank each hide NVLink latency better than a lane with eight — C5 on 8 GPUs: 0.94 vs 2.1 ms per iteration)
   find_warp_ = static_cast<long long>(F_) * 2 * kMaxBatch > 148LL * 8 * 2 && !net_->active();
   if (const char* env = getenv("LGB_B200_FIND_WARP")) find_warp_ = atoi(env) != 0;
+  if (ds_->has_categorical) find_warp_ = false;      // the categorical search exists in the CTA form only
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -197,7 +200,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // tree arrays blob: 8 int arrays [L], decision_type [L], split_gain [L], 4 double arrays [L]
   {
     const size_t ints = 8 * sizeof(int) * L, chars = RoundUp<size_t>(L, 8), floats = RoundUp<size_t>(sizeof(float) * L, 8), dbl = 4 * sizeof(double) * L;
-    tree_blob_bytes_ = dbl + ints + floats + chars;
+    tree_cat_off_ = dbl + ints + floats + chars;      // categorical features: [L][8] words behind the other arrays
+    tree_blob_bytes_ = tree_cat_off_ + (ds_->has_categorical ? sizeof(unsigned int) * 8 * L : 0);
     d_tree_blob_.AllocZero(tree_blob_bytes_);
     h_tree_blob_.resize(tree_blob_bytes_);
     unsigned char* b = d_tree_blob_.p;
@@ -209,6 +213,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev_.leaf_parent = ip + 6 * L; tree_dev_.leaf_depth = ip + 7 * L;
     tree_dev_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+    tree_dev_.cat_bits = ds_->has_categorical ? reinterpret_cast<unsigned int*>(b + tree_cat_off_) : nullptr;
   }
   if (boost_ == kDART) {      // a second set of tree arrays for the earlier trees DART re-adds to the scores
     d_tree_blob2_.AllocZero(tree_blob_bytes_);
@@ -223,6 +228,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     tree_dev2_.leaf_parent = ip + 6 * L; tree_dev2_.leaf_depth = ip + 7 * L;
     tree_dev2_.split_gain = reinterpret_cast<float*>(b + dbl + ints);
     tree_dev2_.decision_type = reinterpret_cast<signed char*>(b + dbl + ints + floats);
+    tree_dev2_.cat_bits = ds_->has_categorical ? reinterpret_cast<unsigned int*>(b + tree_cat_off_) : nullptr;
   }
   SetSmem(k_bt_select, SelectSmemBytes(1024));   // the largest tree the learner accepts; launches ask for what their num_leaves needs
 #define SET_HIST_SMEM(RR, BPL, FLT) SetSmem(k_bt_hist<RR, BPL, FLT, true>, kHistSmem); SetSmem(k_bt_hist<RR, BPL, FLT, false>, kHistSmem)
@@ -752,6 +758,11 @@ void Booster::AddHostTreeToScores(const HostTree& t, int cls, bool train, bool v
     ip[i] = t.left_child[i]; ip[L + i] = t.right_child[i]; ip[2 * L + i] = t.split_feature_inner[i]; ip[3 * L + i] = t.threshold_in_bin[i];
     cp[i] = t.decision_type[i];
   }
+  if (ds_->has_categorical) {
+    unsigned int* cb = reinterpret_cast<unsigned int*>(b + tree_cat_off_);
+    LGB_CHECK(t.num_cat == 0 || static_cast<int>(t.cat_bits_inner.size()) == 8 * (nl - 1), "this tree was not trained by this booster (no bin-level category sets)");
+    for (int i = 0; i < 8 * (nl - 1); ++i) cb[i] = t.num_cat > 0 ? t.cat_bits_inner[i] : 0u;
+  }
   LGB_CUDA(cudaMemcpyAsync(d_tree_blob2_.p, b, tree_blob_bytes_, cudaMemcpyHostToDevice, stream_));
   LGB_CUDA(cudaStreamSynchronize(stream_));      // the host blob is reused by the next tree
   const ScoreMix plain{1.0, 1.0, 0.0, 0};
@@ -760,9 +771,10 @@ void Booster::AddHostTreeToScores(const HostTree& t, int cls, bool train, bool v
     if (n == 0) return;
     const BinLayout& lay = d->layout;
     const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
-#define APPLY_P(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), score, \
+#define APPLY_P(WPR, CAT) k_bt_apply_tree<0, WPR, CAT><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), score, \
         nullptr, nullptr, nullptr, nullptr, tree_dev2_, ds_->d_fmeta.p, static_cast<BatchCtrl*>(nullptr), 1.0, n, cfg_.sigmoid, 1.0, 1.0, plain, nl)
-    if (lay.rm_stride == 32) APPLY_P(8); else if (lay.rm_stride == 64) APPLY_P(16); else APPLY_P(0);
+    if (ds_->has_categorical) { if (lay.rm_stride == 32) APPLY_P(8, true); else if (lay.rm_stride == 64) APPLY_P(16, true); else APPLY_P(0, true); }
+    else if (lay.rm_stride == 32) APPLY_P(8, false); else if (lay.rm_stride == 64) APPLY_P(16, false); else APPLY_P(0, false);
 #undef APPLY_P
     ++launches_;
   };
@@ -1036,11 +1048,33 @@ bool Booster::FetchTree(HostTree* t) {
   t->split_gain.assign(fp, fp + ni);
   t->decision_type.assign(cp, cp + ni);
   t->split_feature.resize(ni); t->threshold.resize(ni);
+  t->num_cat = 0; t->cat_boundaries.assign(1, 0); t->cat_threshold.clear(); t->cat_bits_inner.clear();
+  const unsigned int* cb = ds_->has_categorical ? reinterpret_cast<const unsigned int*>(b + tree_cat_off_) : nullptr;
   for (int i = 0; i < ni; ++i) {
     const int inner = t->split_feature_inner[i];
+    const BinMapperH& m = ds_->mappers[ds_->used[inner]];
     t->split_feature[i] = ds_->used[inner];
-    t->threshold[i] = ds_->mappers[ds_->used[inner]].upper[t->threshold_in_bin[i]];   // RealThreshold
+    if (t->decision_type[i] & 1) {
+      // Tree::SplitCategorical: the node's threshold is its index among the tree's categorical splits; the bins of the split become
+      // a bitset over their category values (SerialTreeLearner::SplitInner: RealThreshold of every bin, Common::ConstructBitset)
+      LGB_CHECK(cb != nullptr, "categorical node in a tree of a dataset without categorical features");
+      std::vector<uint32_t> bits;
+      for (int bin = 1; bin < m.num_bin; ++bin) {
+        if (!((cb[i * 8 + (bin >> 5)] >> (bin & 31)) & 1u)) continue;
+        const int cat = m.bin_2_cat[bin];
+        if (static_cast<int>(bits.size()) < cat / 32 + 1) bits.resize(cat / 32 + 1, 0u);
+        bits[cat / 32] |= 1u << (cat % 32);
+      }
+      t->threshold[i] = t->num_cat;
+      t->threshold_in_bin[i] = t->num_cat;
+      ++t->num_cat;
+      t->cat_boundaries.push_back(t->cat_boundaries.back() + static_cast<int>(bits.size()));
+      t->cat_threshold.insert(t->cat_threshold.end(), bits.begin(), bits.end());
+    } else {
+      t->threshold[i] = m.upper[t->threshold_in_bin[i]];   // RealThreshold
+    }
   }
+  if (t->num_cat > 0) t->cat_bits_inner.assign(cb, cb + 8 * ni);
   return true;
 }
 
@@ -1058,13 +1092,15 @@ void Booster::UpdateScores() {
   if (obj != 0) LGB_CUDA(cudaMemsetAsync(&d_ctrl_->max_abs_g_bits, 0, 2 * sizeof(unsigned int), stream_));
 #define APPLY_ARGS ds_->d_rm.p, static_cast<unsigned>(lay.rm_stride), d_score_.p + cls_ * n_, ds_->d_label.p, w, g, h, tree_dev_, ds_->d_fmeta.p, d_ctrl_, \
                    shrinkage_rate_, n, cfg_.sigmoid, label_weights_[0], label_weights_[1], mix_, 0
-#define APPLY(OBJ)                                                                                              \
-  do {                                                                                                          \
-    if (lay.rm_stride == 32) k_bt_apply_tree<OBJ, 8><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);          \
-    else if (lay.rm_stride == 64) k_bt_apply_tree<OBJ, 16><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);    \
-    else k_bt_apply_tree<OBJ, 0><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);                              \
+#define APPLY_C(OBJ, CAT)                                                                                            \
+  do {                                                                                                               \
+    if (lay.rm_stride == 32) k_bt_apply_tree<OBJ, 8, CAT><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);          \
+    else if (lay.rm_stride == 64) k_bt_apply_tree<OBJ, 16, CAT><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);    \
+    else k_bt_apply_tree<OBJ, 0, CAT><<<grid, kApplyThreads, 0, stream_>>>(APPLY_ARGS);                              \
   } while (0)
+#define APPLY(OBJ) do { if (ds_->has_categorical) APPLY_C(OBJ, true); else APPLY_C(OBJ, false); } while (0)
   if (obj == 1) APPLY(1); else if (obj == 2) APPLY(2); else APPLY(0);
+#undef APPLY_C
 #undef APPLY
 #undef APPLY_ARGS
   ApplyTreeToValidSets();
@@ -1082,9 +1118,10 @@ void Booster::ApplyTreeToValidSets() {
     if (n == 0) continue;
     const BinLayout& lay = d->layout;
     const int grid = std::min(CeilDiv(n, kApplyThreads), kNumSms * 8);
-#define APPLY_V(WPR) k_bt_apply_tree<0, WPR><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p + cls_ * d->num_data, \
+#define APPLY_V(WPR, CAT) k_bt_apply_tree<0, WPR, CAT><<<grid, kApplyThreads, 0, stream_>>>(d->d_rm.p, static_cast<unsigned>(lay.rm_stride), v.score.p + cls_ * d->num_data, \
         nullptr, nullptr, nullptr, nullptr, tree_dev_, ds_->d_fmeta.p, d_ctrl_, shrinkage_rate_, n, cfg_.sigmoid, 1.0, 1.0, mix_, 0)
-    if (lay.rm_stride == 32) APPLY_V(8); else if (lay.rm_stride == 64) APPLY_V(16); else APPLY_V(0);
+    if (ds_->has_categorical) { if (lay.rm_stride == 32) APPLY_V(8, true); else if (lay.rm_stride == 64) APPLY_V(16, true); else APPLY_V(0, true); }
+    else if (lay.rm_stride == 32) APPLY_V(8, false); else if (lay.rm_stride == 64) APPLY_V(16, false); else APPLY_V(0, false);
 #undef APPLY_V
     ++launches_;
   }
@@ -1286,7 +1323,12 @@ ModelHeader Booster::MakeHeader() const {
   h.feature_names = ds_->feature_names;
   for (int j = 0; j < ds_->num_total_features; ++j) {
     const BinMapperH& m = ds_->mappers[j];
-    h.feature_infos.push_back(m.is_trivial ? std::string("none") : "[" + FormatG17(m.min_val) + ":" + FormatG17(m.max_val) + "]");
+    if (m.is_trivial) h.feature_infos.push_back("none");
+    else if (m.bin_type != 0) {      // BinMapper::bin_info_string, categorical: the categories of the bins joined by ':'
+      std::string v;
+      for (size_t b = 0; b < m.bin_2_cat.size(); ++b) { if (b) v.push_back(':'); v += std::to_string(m.bin_2_cat[b]); }
+      h.feature_infos.push_back(v);
+    } else h.feature_infos.push_back("[" + FormatG17(m.min_val) + ":" + FormatG17(m.max_val) + "]");
   }
   for (auto& kv : cfg_.raw) h.parameters.emplace_back(kv.first, kv.second);
   return h;
@@ -1411,11 +1453,19 @@ void Booster::UploadModel() {
   std::vector<int> node_off(1, 0), leaf_off(1, 0), feat, left, right, icount, lcount, depth;
   std::vector<double> thr, leaf, expected;
   std::vector<signed char> dt;
+  std::vector<int> cat_begin, cat_words;      // per node: its category set in cat_thr (categorical nodes), else 0 / 0
+  std::vector<unsigned int> cat_thr;
   model_max_depth_ = 0;
   for (const HostTree& t : models_) {
     const int ni = t.num_leaves - 1;
     const bool has_counts = static_cast<int>(t.internal_count.size()) == ni && static_cast<int>(t.leaf_count.size()) == t.num_leaves;
+    const int cat_base = static_cast<int>(cat_thr.size());
+    if (ni > 0) cat_thr.insert(cat_thr.end(), t.cat_threshold.begin(), t.cat_threshold.end());
     for (int i = 0; i < ni; ++i) {
+      if (t.decision_type[i] & 1) {
+        const int k = static_cast<int>(t.threshold[i]);
+        cat_begin.push_back(cat_base + t.cat_boundaries[k]); cat_words.push_back(t.cat_boundaries[k + 1] - t.cat_boundaries[k]);
+      } else { cat_begin.push_back(0); cat_words.push_back(0); }
       feat.push_back(t.split_feature[i]); thr.push_back(t.threshold[i]); dt.push_back(t.decision_type[i]);
       left.push_back(t.left_child[i]); right.push_back(t.right_child[i]);
       icount.push_back(has_counts ? t.internal_count[i] : 0);
@@ -1447,6 +1497,7 @@ void Booster::UploadModel() {
     if (!v.empty()) LGB_CUDA(cudaMemcpyAsync(buf.p, v.data(), sizeof(v[0]) * v.size(), cudaMemcpyHostToDevice, stream_));
   };
   up(dp_node_off_, node_off); up(dp_leaf_off_, leaf_off); up(dp_feat_, feat); up(dp_left_, left); up(dp_right_, right);
+  up(dp_cat_begin_, cat_begin); up(dp_cat_words_, cat_words); up(dp_cat_thr_, cat_thr);
   up(dp_thr_, thr); up(dp_leaf_, leaf); up(dp_dt_, dt); up(dp_icount_, icount); up(dp_lcount_, lcount); up(dp_expected_, expected); up(dp_depth_, depth);
   LGB_CUDA(cudaStreamSynchronize(stream_));      // the host vectors go out of scope
   uploaded_version_ = model_version_;
@@ -1472,6 +1523,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   m.node_off = dp_node_off_.p; m.leaf_off = dp_leaf_off_.p; m.split_feature = dp_feat_.p; m.threshold = dp_thr_.p;
   m.decision_type = dp_dt_.p; m.left = dp_left_.p; m.right = dp_right_.p; m.leaf_value = dp_leaf_.p;
   m.internal_count = dp_icount_.p; m.leaf_count = dp_lcount_.p; m.expected = dp_expected_.p; m.max_depth = dp_depth_.p;
+  m.cat_begin = dp_cat_begin_.p; m.cat_words = dp_cat_words_.p; m.cat_threshold = dp_cat_thr_.p;
   // feature contributions: TreeSHAP recurses to the depth of the deepest tree and keeps (D + 1)(D + 2) / 2 path elements per thread
   const int shap_threads = kNumSms * 2 * 128;
   const int path_elems = (model_max_depth_ + 1) * (model_max_depth_ + 2) / 2;

@@ -28,6 +28,10 @@ struct SplitDev {
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
   long long left_int_g, left_int_h, right_int_g, right_int_h;
   int missing_type, nan_bin;   // of the split feature (nan_bin = -1: none), so that later stages need no feature table lookup
+  // categorical split: the rows whose bin has its bit set in cat_bits go left, everything else (bin 0 included) right; threshold,
+  // default_left and nan_bin are unused
+  int is_cat, pad_;
+  unsigned int cat_bits[8];
 };
 
 // ---- peer-memory exchange of the data-parallel learner (kernels: batch_tree.cuh) ------------------------------------------
@@ -91,6 +95,7 @@ struct TreeArraysDev {
   signed char* decision_type;
   float* split_gain;
   double *leaf_value, *leaf_weight, *internal_value, *internal_weight;
+  unsigned int* cat_bits;      // [L][8]: the bins that go left at a categorical node (nullptr: the dataset has no categorical feature)
 };
 
 struct LearnerParams {
@@ -101,6 +106,9 @@ struct LearnerParams {
   int reduce_in_select;                   // few features: the replay kernel reduces the per-feature results of a child (no last-arriver
                                           // reduction at the end of the split search)
   const unsigned char* feature_mask;      // [F] 1 = this tree may split on the feature (feature_fraction < 1), nullptr = all
+  // categorical split search (upstream config.h: max_cat_to_onehot, max_cat_threshold, min_data_per_group, cat_smooth, cat_l2)
+  int max_cat_to_onehot, max_cat_threshold, min_data_per_group;
+  double cat_smooth, cat_l2;
 };
 
 class Booster {
@@ -212,6 +220,8 @@ class Booster {
   ModelHeader loaded_header_;
   long long model_version_ = 0, uploaded_version_ = -1;
   DevBuf<int> dp_node_off_, dp_leaf_off_, dp_feat_, dp_left_, dp_right_, dp_icount_, dp_lcount_, dp_depth_;
+  DevBuf<int> dp_cat_begin_, dp_cat_words_;      // categorical nodes: first word / number of words of the node's category set
+  DevBuf<unsigned int> dp_cat_thr_;
   DevBuf<double> dp_expected_;
   DevBuf<unsigned char> dp_paths_;         // feature contributions: the threads' TreeSHAP paths
   int model_max_depth_ = 0;
@@ -275,6 +285,7 @@ class Booster {
   DevBuf<unsigned char> d_tree_blob_;
   TreeArraysDev tree_dev_{};
   size_t tree_blob_bytes_ = 0;
+  size_t tree_cat_off_ = 0;          // offset of the [L][8] category-set words in the tree blob (present with categorical features)
   std::vector<unsigned char> h_tree_blob_;
   // lambdarank
   DevBuf<double> d_sigmoid_table_, d_inv_max_dcg_, d_label_gain_, d_discount_;

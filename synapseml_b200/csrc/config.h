@@ -65,7 +65,11 @@ struct Config {
   bool lambdarank_norm = true;
   std::vector<double> label_gain;
   std::vector<int> eval_at;
+  // categorical features: column indexes (LightGBMBase.scala:162-198 resolves slot names to indexes before the native call) and the
+  // knobs of the categorical split search (upstream config.h defaults; CategoricalParams in params/TrainParams.scala)
   std::vector<int> categorical_feature;
+  int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
+  double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // canonical key -> value as received (echoed into the model's parameters block)
 
   void Set(const std::string& params);      // merges; keys already present in `params` earlier win over later ones

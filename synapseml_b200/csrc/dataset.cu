@@ -45,7 +45,7 @@ struct K1Params {
 };
 
 struct K1Meta {
-  int num_bin, missing_type, is_trivial, default_bin, most_freq_bin, pad;
+  int num_bin, missing_type, is_trivial, default_bin, most_freq_bin, bin_type;
   double sparse_rate, min_val, max_val;
 };
 
@@ -308,6 +308,68 @@ __device__ int K1ZeroAsOneBinBlock(const double* dv, const int* cnt, int nd, int
   return nb;
 }
 
+// Categorical feature (BinMapper::FindBin, bin_type == CategoricalBin), by the whole CTA.  dv / dc: the distinct sampled values
+// (ascending) and their counts; ci: scratch for the category values.  The values are cut to ints (negative ones, and values beyond
+// int, count as missing), equal neighbours merged, and the categories taken by falling count (ties: the smaller value first — the
+// stable sort upstream) until 99 % of the non-missing sample is covered AND max_bin bins exist; a category seen fewer than
+// min_data_in_bin times ends the list (except the first two).  Bin 0 collects everything else.  Every pick is a block-wide
+// arg-max over the categories not taken yet.  out[b]: category of bin b (out[0] = -1); c[b]: sample rows of bin b.  Returns
+// num_bin (0: no non-missing value; kMaxBinsPerFeature + 1: more categories than the uint8 bin matrix holds).
+__device__ int K1CategoricalBlock(const double* dv, int* dc, int* ci, int nd, int na_cnt, const K1Params& p, double* out, int* c,
+                                  int* missing_type) {
+  __shared__ int s_n, s_na;
+  __shared__ long long s_best[kK1Threads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    int n = 0, na = na_cnt;
+    for (int i = 0; i < nd; ++i) {
+      const double x = dv[i];
+      const int val = x < 2147483648.0 ? static_cast<int>(x) : -1;
+      const int cnt = dc[i];
+      if (val < 0) na += cnt;
+      else if (n == 0 || val != ci[n - 1]) { ci[n] = val; dc[n] = cnt; ++n; }      // in place: n <= i
+      else dc[n - 1] += cnt;
+    }
+    s_n = n; s_na = na;
+  }
+  __syncthreads();
+  const int n = s_n, na = s_na;
+  const int rest_cnt = p.total_sample_cnt - na;
+  if (rest_cnt <= 0) return 0;
+  const int cut_cnt = static_cast<int>(static_cast<double>(__fmul_rn(static_cast<float>(rest_cnt), 0.99f)) + 0.5f);
+  int distinct_cnt = n;
+  if (na > 0) ++distinct_cnt;
+  const int max_bin = min(distinct_cnt, p.max_bin);
+  int num_bin = 1, used_cnt = 0, cur_cat = 0;
+  if (tid == 0) { out[0] = -1.0; c[0] = 0; }
+  while (cur_cat < n && (used_cnt < cut_cnt || num_bin < max_bin)) {
+    // arg-max of (count, then the smaller index) over the categories not taken yet (taken: count -1)
+    long long best = -1;
+    for (int i = tid; i < n; i += kK1Threads) {
+      const int cnt = dc[i];
+      if (cnt >= 0) { const long long key = (static_cast<long long>(cnt) << 32) | static_cast<unsigned>(0x7fffffff - i); if (key > best) best = key; }
+    }
+    for (int o = 16; o > 0; o >>= 1) { const long long t = __shfl_xor_sync(0xffffffffu, best, o); if (t > best) best = t; }
+    if (lane == 0) s_best[warp] = best;
+    __syncthreads();
+    best = s_best[0];
+    for (int w = 1; w < kK1Threads / 32; ++w) if (s_best[w] > best) best = s_best[w];
+    __syncthreads();
+    const int cnt = static_cast<int>(best >> 32), idx = 0x7fffffff - static_cast<int>(best & 0xffffffffLL);
+    if (cnt < p.min_data_in_bin && cur_cat > 1) break;
+    if (num_bin >= kMaxBinsPerFeature) return kMaxBinsPerFeature + 1;
+    if (tid == 0) { out[num_bin] = static_cast<double>(ci[idx]); c[num_bin] = cnt; dc[idx] = -1; }
+    __syncthreads();
+    used_cnt += cnt;
+    ++num_bin;
+    ++cur_cat;
+  }
+  *missing_type = (cur_cat == n && na == 0) ? kMissingNone : kMissingNaN;
+  if (tid == 0) c[0] = p.total_sample_cnt - used_cnt;
+  __syncthreads();
+  return num_bin;
+}
+
 // sorted: every feature's segment sorted ascending, NaNs last.  distinct/counts/starts: scratch with room for n_f + 2 per
 // feature (offset seg_off[f] + 2 f).  bounds/tmp/upper/lower/cib: [F][bstride].
 // One CTA per feature.  The O(n_sample) part — runs of (ulp-)equal values -> distinct values + counts, with the implicit
@@ -316,7 +378,8 @@ __device__ int K1ZeroAsOneBinBlock(const double* dv, const int* cnt, int nd, int
 // accumulators (no read-modify-write of global memory inside its loops).
 __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, const long long* seg_off, const int* na_cnt_arr, int nfeat,
                                                         K1Params p, double* distinct, int* counts, int* starts, double* bounds, double* tmp,
-                                                        double* upper, double* lower, int* cib, K1Meta* meta) {
+                                                        double* upper, double* lower, int* cib, K1Meta* meta,
+                                                        const unsigned char* __restrict__ is_cat) {
   const int f = blockIdx.x;
   if (f >= nfeat) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -391,7 +454,11 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   double* up = upper + (long long)f * p.bstride;
   double* lo = lower + (long long)f * p.bstride;
   int num_bin;
-  if (missing_type == kMissingZero) {
+  const bool cat = is_cat != nullptr && is_cat[f] != 0;
+  int* c = cib + (long long)f * p.bstride;
+  if (cat) {
+    num_bin = K1CategoricalBlock(dv, dc, st, nd, na_cnt, p, out, c, &missing_type);
+  } else if (missing_type == kMissingZero) {
     num_bin = K1ZeroAsOneBinBlock(dv, dc, nd, p.max_bin, p.total_sample_cnt, p.min_data_in_bin, out, t, up, lo, &k1sh);
     if (num_bin == 2) missing_type = kMissingNone;
   } else if (missing_type == kMissingNone) {
@@ -403,10 +470,9 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   }
   // rows of the sample per bin: every distinct value goes to the first bin whose upper bound is not below it (the last bin
   // otherwise) — what the sequential sweep computes, done with a binary search per value and integer atomics
-  int* c = cib + (long long)f * p.bstride;
-  for (int i = tid; i < num_bin; i += kK1Threads) c[i] = 0;
-  __syncthreads();
-  {
+  if (!cat) {
+    for (int i = tid; i < num_bin; i += kK1Threads) c[i] = 0;
+    __syncthreads();
     const int last = num_bin - 1;
     for (int i = tid; i < nd; i += kK1Threads) {
       const double x = dv[i];
@@ -420,17 +486,29 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   }
   __syncthreads();
   if (tid != 0) return;
-  if (missing_type == kMissingNaN) c[num_bin - 1] = na_cnt;
+  if (!cat && missing_type == kMissingNaN) c[num_bin - 1] = na_cnt;
   K1Meta m;
   m.min_val = dv[0];
   m.max_val = dv[nd - 1];
+  m.bin_type = cat ? 1 : 0;
   int is_trivial = num_bin <= 1;
-  if (!is_trivial && p.pre_filter) {
+  if (!is_trivial && p.pre_filter && num_bin <= kMaxBinsPerFeature) {
+    // NeedFilter: numerical — no cut leaves filter_cnt sample rows on both sides; categorical — with at most two bins, no bin
+    // against the rest does (more bins are never filtered)
     bool need = true;
     int sum_left = 0;
-    for (int i = 0; i + 1 < num_bin; ++i) {
-      sum_left += c[i];
-      if (sum_left >= p.filter_cnt && p.total_sample_cnt - sum_left >= p.filter_cnt) { need = false; break; }
+    if (!cat) {
+      for (int i = 0; i + 1 < num_bin; ++i) {
+        sum_left += c[i];
+        if (sum_left >= p.filter_cnt && p.total_sample_cnt - sum_left >= p.filter_cnt) { need = false; break; }
+      }
+    } else if (num_bin <= 2) {
+      for (int i = 0; i + 1 < num_bin; ++i) {
+        sum_left = c[i];
+        if (sum_left >= p.filter_cnt && p.total_sample_cnt - sum_left >= p.filter_cnt) { need = false; break; }
+      }
+    } else {
+      need = false;
     }
     if (need) is_trivial = 1;
   }
@@ -440,8 +518,9 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   m.default_bin = 0;
   m.most_freq_bin = 0;
   m.sparse_rate = 1.0;
-  if (!is_trivial) {
-    m.default_bin = K1ValueToBin(0.0, out, num_bin, missing_type);
+  if (!is_trivial && num_bin <= kMaxBinsPerFeature) {
+    if (cat) { for (int i = 1; i < num_bin; ++i) if (out[i] == 0.0) m.default_bin = i; }      // the bin of category 0, if it has one
+    else m.default_bin = K1ValueToBin(0.0, out, num_bin, missing_type);
     int arg = 0;
     for (int i = 1; i < num_bin; ++i) if (c[i] > c[arg]) arg = i;
     const double max_sparse_rate = (double)c[arg] / p.total_sample_cnt;
@@ -449,7 +528,6 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
     m.most_freq_bin = arg;
     m.sparse_rate = (double)c[arg] / p.total_sample_cnt;
   }
-  m.pad = 0;
   meta[f] = m;
 }
 
@@ -468,23 +546,33 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
 constexpr int K2_ROWS = 128;
 constexpr int K2_FT = 32;
 
+// CAT: the dataset has categorical features.  Such a feature's row of `bounds` holds its kept categories in ascending order and
+// `catbin` the bin of each (BinMapper::ValueToBin, categorical: the value is cut to an int; NaN, negative and unlisted values
+// are bin 0): the same lower-bound search finds the slot, an equality test and one byte load finish it.
+template <bool CAT>
 __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ data, int nrow, int ncol, long long start_row,
                                                    const double* __restrict__ bounds, const FeatureMetaDev* __restrict__ fmeta,
                                                    int f_used, uint8_t* __restrict__ cm, long long n_pad,
-                                                   uint8_t* __restrict__ rm, int rm_stride) {
+                                                   uint8_t* __restrict__ rm, int rm_stride, const uint8_t* __restrict__ catbin) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sb = reinterpret_cast<double*>(smem_raw);                                       // [256 bins][32 features]
   uint8_t* tile_rm = smem_raw + sizeof(double) * K2_FT * kMaxBinsPerFeature;              // [128 rows][32 features]
+  uint8_t* scb = tile_rm + K2_FT * K2_ROWS;                                               // CAT: [256 slots][32 features]
   const int ft = blockIdx.y;
   const int f0 = ft * K2_FT;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < K2_FT * kMaxBinsPerFeature; i += blockDim.x) {
     const int f = i >> 8, b = i & 255;      // consecutive threads read consecutive bins of one feature (coalesced)
     sb[b * K2_FT + f] = (f0 + f < f_used) ? bounds[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0.0;
+    if (CAT) scb[b * K2_FT + f] = (f0 + f < f_used) ? catbin[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0;
   }
   const int fi = f0 + lane;
   int num_bin = 1, missing_type = 0, real = 0;
-  if (fi < f_used) { num_bin = fmeta[fi].num_bin; missing_type = fmeta[fi].missing_type; real = fmeta[fi].real_index; }
+  bool is_cat = false;
+  if (fi < f_used) {
+    num_bin = fmeta[fi].num_bin; missing_type = fmeta[fi].missing_type; real = fmeta[fi].real_index;
+    if (CAT && fmeta[fi].bin_type != 0) { is_cat = true; num_bin -= 1; missing_type = kMissingNone; }      // search the num_bin - 1 categories
+  }
   __syncthreads();
   const long long first_blk = start_row / K2_ROWS;
   const long long last_blk = (start_row + nrow - 1) / K2_ROWS;
@@ -502,9 +590,15 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
       lo_[k] = 0;
       hi_[k] = in ? (missing_type == kMissingNaN ? num_bin - 2 : num_bin - 1) : 0;
     }
+    unsigned int unlisted = 0;      // CAT: rows whose value is no category at all
     #pragma unroll
     for (int k = 0; k < 16; ++k) {
-      if (val[k] != val[k]) {      // NaN: the last bin when the feature has a NaN bin, else it is binned as 0.0
+      if (CAT && is_cat) {
+        const double v = val[k];
+        const bool ok = v == v && v < 2147483648.0 && static_cast<int>(v) >= 0;
+        if (!ok) unlisted |= 1u << k;
+        val[k] = ok ? static_cast<double>(static_cast<int>(v)) : 0.0;
+      } else if (val[k] != val[k]) {      // NaN: the last bin when the feature has a NaN bin, else it is binned as 0.0
         if (missing_type == kMissingNaN) { lo_[k] = hi_[k] = num_bin - 1; }
         else val[k] = 0.0;
       }
@@ -519,6 +613,13 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
         const bool le = val[k] <= myb[(go ? m : 0) * K2_FT];
         hi_[k] = (go && le) ? m : r;
         lo_[k] = (go && !le) ? m + 1 : l;
+      }
+    }
+    if (CAT && is_cat) {
+      #pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const bool hit = !((unlisted >> k) & 1u) && myb[lo_[k] * K2_FT] == val[k];
+        lo_[k] = hit ? static_cast<int>(scb[lo_[k] * K2_FT + lane]) : 0;
       }
     }
     unsigned int w[4];
@@ -591,10 +692,23 @@ void Dataset::FinishSchema() {
   std::vector<double> hb(static_cast<size_t>(std::max(F, 1)) * kMaxBinsPerFeature, std::numeric_limits<double>::infinity());
   std::vector<FeatureMetaDev> hm(std::max(F, 1));
   std::vector<int> hr(std::max(F, 1), 0);
+  std::vector<uint8_t> hcb(hb.size(), 0);
+  has_categorical = false;
   for (int i = 0; i < F; ++i) {
     const BinMapperH& m = mappers[used[i]];
-    for (int b = 0; b < m.num_bin; ++b) hb[static_cast<size_t>(i) * kMaxBinsPerFeature + b] = m.upper[b];
-    hm[i] = FeatureMetaDev{m.num_bin, m.missing_type, m.default_bin, m.most_freq_bin, used[i], {0, 0, 0}};
+    if (m.bin_type != 0) {      // categorical: the kept categories in ascending order and the bin of each (the row-binning kernel's search)
+      std::vector<std::pair<int, int>> cb;
+      for (int b = 1; b < m.num_bin; ++b) cb.emplace_back(m.bin_2_cat[b], b);
+      std::sort(cb.begin(), cb.end());
+      for (size_t k = 0; k < cb.size(); ++k) {
+        hb[static_cast<size_t>(i) * kMaxBinsPerFeature + k] = static_cast<double>(cb[k].first);
+        hcb[static_cast<size_t>(i) * kMaxBinsPerFeature + k] = static_cast<uint8_t>(cb[k].second);
+      }
+      has_categorical = true;
+    } else {
+      for (int b = 0; b < m.num_bin; ++b) hb[static_cast<size_t>(i) * kMaxBinsPerFeature + b] = m.upper[b];
+    }
+    hm[i] = FeatureMetaDev{m.num_bin, m.missing_type, m.default_bin, m.most_freq_bin, used[i], m.bin_type, {0, 0}};
     hr[i] = used[i];
   }
   LGB_CUDA(cudaSetDevice(device));
@@ -602,6 +716,10 @@ void Dataset::FinishSchema() {
   LGB_CUDA(cudaMemcpy(d_bounds.p, hb.data(), hb.size() * sizeof(double), cudaMemcpyHostToDevice));
   d_fmeta.Alloc(hm.size());
   LGB_CUDA(cudaMemcpy(d_fmeta.p, hm.data(), hm.size() * sizeof(FeatureMetaDev), cudaMemcpyHostToDevice));
+  if (has_categorical) {
+    d_catbin.Alloc(hcb.size());
+    LGB_CUDA(cudaMemcpy(d_catbin.p, hcb.data(), hcb.size(), cudaMemcpyHostToDevice));
+  }
   d_real_index.Alloc(hr.size());
   LGB_CUDA(cudaMemcpy(d_real_index.p, hr.data(), hr.size() * sizeof(int), cudaMemcpyHostToDevice));
 }
@@ -630,7 +748,12 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   const Config& c = ds->cfg;
   LGB_CHECK(ncol > 0, "ncol must be positive");
   LGB_CHECK(c.max_bin >= 2 && c.max_bin <= 255, "max_bin=%d is outside [2, 255] (uint8 bin storage)", c.max_bin);
-  LGB_CHECK(c.categorical_feature.empty(), "categorical_feature is not supported by this library yet");
+  std::vector<unsigned char> h_is_cat(ncol, 0);
+  for (int j : c.categorical_feature) {
+    LGB_CHECK(j >= 0 && j < ncol, "categorical_feature=%d is not a column index (0..%d)", j, ncol - 1);
+    h_is_cat[j] = 1;
+  }
+  const bool any_cat = !c.categorical_feature.empty();
   ds->device = ResolveDevice(c);
   LGB_CUDA(cudaSetDevice(ds->device));
   ds->num_total_features = ncol;
@@ -673,7 +796,12 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   p.use_missing = c.use_missing;
   p.zero_as_missing = c.zero_as_missing;
   p.total_sample_cnt = num_sample_row;
-  p.bstride = c.max_bin + 4;
+  p.bstride = any_cat ? std::max(c.max_bin + 4, kMaxBinsPerFeature + 4) : c.max_bin + 4;      // a categorical feature may exceed max_bin bins
+  DevBuf<unsigned char> d_is_cat;
+  if (any_cat) {
+    d_is_cat.Alloc(ncol);
+    LGB_CUDA(cudaMemcpy(d_is_cat.p, h_is_cat.data(), ncol, cudaMemcpyHostToDevice));
+  }
   d_distinct.Alloc(total + 2LL * ncol + 2);
   d_counts.Alloc(total + 2LL * ncol + 2);
   d_starts.Alloc(total + 2LL * ncol + 2);
@@ -681,7 +809,7 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   d_bnd.Alloc(bs); d_tmp.Alloc(bs); d_up.Alloc(bs); d_lo.Alloc(bs); d_cib.Alloc(bs);
   d_meta.Alloc(ncol);
   k1_find_bin<<<ncol, kK1Threads>>>(d_sorted.p, d_off.p, d_na.p, ncol, p, d_distinct.p, d_counts.p, d_starts.p, d_bnd.p, d_tmp.p,
-                                    d_up.p, d_lo.p, d_cib.p, d_meta.p);
+                                    d_up.p, d_lo.p, d_cib.p, d_meta.p, any_cat ? d_is_cat.p : nullptr);
   LGB_CUDA(cudaGetLastError());
   LGB_CUDA(cudaDeviceSynchronize());
   std::vector<K1Meta> hmeta(ncol);
@@ -694,7 +822,14 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
     m.num_bin = hmeta[j].num_bin; m.missing_type = hmeta[j].missing_type; m.is_trivial = hmeta[j].is_trivial;
     m.default_bin = hmeta[j].default_bin; m.most_freq_bin = hmeta[j].most_freq_bin; m.sparse_rate = hmeta[j].sparse_rate;
     m.min_val = hmeta[j].min_val; m.max_val = hmeta[j].max_val;
+    m.bin_type = hmeta[j].bin_type;
+    LGB_CHECK(m.num_bin <= kMaxBinsPerFeature,
+              "Categorical feature %d needs more than %d bins; only uint8 bin storage is built in this version", j, kMaxBinsPerFeature);
     m.upper.assign(hb.begin() + static_cast<size_t>(j) * p.bstride, hb.begin() + static_cast<size_t>(j) * p.bstride + m.num_bin);
+    if (m.bin_type != 0) {      // the "bounds" of a categorical feature are the categories of its bins
+      m.bin_2_cat.resize(m.num_bin);
+      for (int b = 0; b < m.num_bin; ++b) m.bin_2_cat[b] = static_cast<int>(m.upper[b]);
+    }
   }
   ds->FinishSchema();
   ds->AllocateRows(num_local_row);
@@ -720,12 +855,13 @@ constexpr uint32_t kRefMagic = 0x4C42B200u;
 std::string Dataset::SerializeReference() const {
   Writer w;
   w.Put<uint32_t>(kRefMagic);
-  w.Put<int32_t>(1);
+  w.Put<int32_t>(2);
   w.PutStr(param_string);
   w.Put<int32_t>(num_total_features);
   for (const auto& m : mappers) {
     w.Put<int32_t>(m.num_bin); w.Put<int32_t>(m.missing_type); w.Put<int32_t>(m.is_trivial); w.Put<int32_t>(m.default_bin);
     w.Put<int32_t>(m.most_freq_bin); w.Put<double>(m.sparse_rate); w.Put<double>(m.min_val); w.Put<double>(m.max_val);
+    w.Put<int32_t>(m.bin_type);
     for (double b : m.upper) w.Put<double>(b);
   }
   for (const auto& n : feature_names) w.PutStr(n);
@@ -735,7 +871,7 @@ std::string Dataset::SerializeReference() const {
 Dataset* Dataset::CreateFromSerializedReference(const void* buf, int32_t len, int64_t num_row, const char* params) {
   Reader r{static_cast<const char*>(buf), static_cast<const char*>(buf) + len};
   LGB_CHECK(r.Get<uint32_t>() == kRefMagic, "Buffer is not a serialized reference dataset of this library");
-  LGB_CHECK(r.Get<int32_t>() == 1, "Unsupported serialized reference dataset version");
+  LGB_CHECK(r.Get<int32_t>() == 2, "Unsupported serialized reference dataset version");
   std::unique_ptr<Dataset> ds(new Dataset());
   ds->param_string = r.GetStr();
   ds->cfg.Set(ds->param_string);         // the parameters the reference was built with (driver side) ...
@@ -749,9 +885,14 @@ Dataset* Dataset::CreateFromSerializedReference(const void* buf, int32_t len, in
     m.num_bin = r.Get<int32_t>(); m.missing_type = r.Get<int32_t>(); m.is_trivial = r.Get<int32_t>();
     m.default_bin = r.Get<int32_t>(); m.most_freq_bin = r.Get<int32_t>(); m.sparse_rate = r.Get<double>();
     m.min_val = r.Get<double>(); m.max_val = r.Get<double>();
-    LGB_CHECK(m.num_bin >= 1 && m.num_bin <= 65536, "Corrupt serialized reference dataset");
+    m.bin_type = r.Get<int32_t>();
+    LGB_CHECK(m.num_bin >= 0 && m.num_bin <= 65536 && (m.bin_type == 0 || m.bin_type == 1), "Corrupt serialized reference dataset");
     m.upper.resize(m.num_bin);
     for (auto& b : m.upper) b = r.Get<double>();
+    if (m.bin_type != 0) {
+      m.bin_2_cat.resize(m.num_bin);
+      for (int b = 0; b < m.num_bin; ++b) m.bin_2_cat[b] = static_cast<int>(m.upper[b]);
+    }
   }
   ds->feature_names.resize(ds->num_total_features);
   for (auto& n : ds->feature_names) n = r.GetStr();
@@ -852,6 +993,27 @@ void Dataset::InitStreaming(bool has_w, bool has_init, bool has_q, int nclasses,
   streaming_inited = true;
 }
 
+// One launch of the row-binning kernel over `nrow` staged rows that start at absolute row `start_row`.
+void Dataset::LaunchBinRows(const double* staged, int nrow, long long start_row, cudaStream_t stream) {
+  const int F = num_features();
+  const long long nblk = (start_row + nrow - 1) / K2_ROWS - start_row / K2_ROWS + 1;
+  const int ftiles = CeilDiv(F, K2_FT);
+  dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
+  const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS + (has_categorical ? K2_FT * kMaxBinsPerFeature : 0);
+  static bool attr_set[2] = {false, false};
+  if (!attr_set[has_categorical ? 1 : 0]) {
+    if (has_categorical) LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    else LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    attr_set[has_categorical ? 1 : 0] = true;
+  }
+  if (has_categorical)
+    k2_bin_rows<true><<<grid, 256, smem, stream>>>(staged, nrow, num_total_features, start_row, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p,
+                                                   layout.rm_stride, d_catbin.p);
+  else
+    k2_bin_rows<false><<<grid, 256, smem, stream>>>(staged, nrow, num_total_features, start_row, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p,
+                                                    layout.rm_stride, nullptr);
+}
+
 void Dataset::FlushSlot(PushSlot* s) {
   if (s->seg_rows == 0) return;
   LGB_CUDA(cudaSetDevice(device));
@@ -860,17 +1022,7 @@ void Dataset::FlushSlot(PushSlot* s) {
   LGB_CUDA(cudaMemcpyAsync(s->dstage[k], s->pinned[k], bytes, cudaMemcpyHostToDevice, s->stream));
   const int F = num_features();
   if (F > 0) {
-    const long long nblk = (s->seg_start + s->seg_rows - 1) / K2_ROWS - s->seg_start / K2_ROWS + 1;
-    const int ftiles = CeilDiv(F, K2_FT);
-    dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
-    const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS;
-    static bool attr_set = false;
-    if (!attr_set) {
-      LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      attr_set = true;
-    }
-    k2_bin_rows<<<grid, 256, smem, s->stream>>>(s->dstage[k], static_cast<int>(s->seg_rows), num_total_features, s->seg_start,
-                                                d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+    LaunchBinRows(s->dstage[k], static_cast<int>(s->seg_rows), s->seg_start, s->stream);
     LGB_CUDA(cudaGetLastError());
   }
   LGB_CUDA(cudaEventRecord(s->ev[k], s->stream));
@@ -891,17 +1043,11 @@ float Dataset::TimeBinning(const double* rows, int nrow, int repeats) {
   DevBuf<double> d;
   d.Alloc(static_cast<size_t>(nrow) * num_total_features);
   LGB_CUDA(cudaMemcpy(d.p, rows, sizeof(double) * nrow * num_total_features, cudaMemcpyHostToDevice));
-  const long long nblk = (nrow - 1) / K2_ROWS + 1;
-  const int ftiles = CeilDiv(F, K2_FT);
-  dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
-  const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS;
-  LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   cudaEvent_t e0, e1;
   LGB_CUDA(cudaEventCreate(&e0)); LGB_CUDA(cudaEventCreate(&e1));
-  k2_bin_rows<<<grid, 256, smem, 0>>>(d.p, nrow, num_total_features, 0, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+  LaunchBinRows(d.p, nrow, 0, 0);
   LGB_CUDA(cudaEventRecord(e0, 0));
-  for (int r = 0; r < repeats; ++r)
-    k2_bin_rows<<<grid, 256, smem, 0>>>(d.p, nrow, num_total_features, 0, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p, layout.rm_stride);
+  for (int r = 0; r < repeats; ++r) LaunchBinRows(d.p, nrow, 0, 0);
   LGB_CUDA(cudaEventRecord(e1, 0));
   LGB_CUDA(cudaEventSynchronize(e1));
   LGB_CUDA(cudaGetLastError());

@@ -31,7 +31,9 @@ struct BinMapperH {
   int most_freq_bin = 0;
   double sparse_rate = 1.0;
   double min_val = 0.0, max_val = 0.0;
-  std::vector<double> upper;    // bin_upper_bound[num_bin]
+  std::vector<double> upper;    // bin_upper_bound[num_bin]; categorical: the category of every bin as a double
+  int bin_type = 0;             // 0 numerical, 1 categorical (BinType::CategoricalBin)
+  std::vector<int> bin_2_cat;   // categorical: category of bin b (bin 0: -1 = NaN, negative, rare and unseen categories)
 };
 
 // Per used (inner) feature, device side.
@@ -41,7 +43,8 @@ struct FeatureMetaDev {
   int default_bin;
   int most_freq_bin;
   int real_index;
-  int pad_[3];
+  int bin_type;        // 1: categorical
+  int pad_[2];
 };
 
 // HBM layout of the binned matrix.  Two copies are kept, both written by the K2 kernel in one pass:
@@ -75,6 +78,8 @@ class Dataset {
   DevBuf<FeatureMetaDev> d_fmeta;        // [F_used]
   DevBuf<int> d_real_index;              // [F_used]
   DevBuf<uint8_t> d_cm, d_rm;
+  DevBuf<uint8_t> d_catbin;              // [F_used][kMaxBinsPerFeature]: categorical features — bin of the k-th smallest kept category
+  bool has_categorical = false;
   DevBuf<float> d_label, d_weight;
   DevBuf<double> d_init_score;
   DevBuf<int32_t> d_query_boundaries;
@@ -130,6 +135,7 @@ class Dataset {
   void AllocateRows(int64_t n);
   void EnsureSlots(int n);
   void FlushSlot(PushSlot* s);
+  void LaunchBinRows(const double* staged, int nrow, long long start_row, cudaStream_t stream);
   void FreeSlots();
 };
 

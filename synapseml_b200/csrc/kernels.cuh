@@ -419,6 +419,9 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
   s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
   s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
   s.missing_type = 0; s.nan_bin = -1;
+  s.is_cat = 0; s.pad_ = 0;
+  #pragma unroll
+  for (int i = 0; i < 8; ++i) s.cat_bits[i] = 0u;
   return s;
 }
 
@@ -623,6 +626,211 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
       s.default_left = reverse ? 1 : 0;
     }
     if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    *out = s;
+    *splittable_out = any ? 1 : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K6, categorical features
+// One 256-thread CTA searches one categorical feature of one leaf, one bin per thread (FindBestThresholdCategoricalInner /
+// ...IntInner).  Bin 0 (NaN, negative, rare and unseen categories) is never a candidate and always goes right.
+//   few bins (num_bin <= max_cat_to_onehot): every category alone against the rest, one candidate per thread, block arg-max
+//     (ties: the smaller bin, as the sequential loop's strict '>');
+//   otherwise: the bins with at least cat_smooth rows are ranked by sum_gradient / (sum_hessian + cat_smooth) — every thread counts
+//     the bins that precede its own (ties: the smaller bin first, the stable sort upstream) — and the two prefix scans over that
+//     order, from the front and from the back (at most max_cat_threshold categories, groups of at least min_data_per_group rows,
+//     cat_l2 added to lambda_l2), run sequentially on two threads of different warps: their `continue` / `break` rules carry state
+//     (the size of the current group) from one position to the next, and there are at most 2 x max_cat_threshold positions.
+// QUANT: every sum is int_sum * scale, without the kEpsilon terms of the float form.  Result valid in thread 0.  Uses one set of
+// shared arrays: sub-block 0 only.
+struct CatDirBest { double gain; int thr, left_count; long long ig, ih; double lg, lh; };
+
+template <bool QUANT>
+__device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
+                                 long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
+                                 double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
+                                 long long* out_tot_g, long long* out_tot_h, int sub) {
+  __shared__ long long s_g[8], s_h[8];
+  __shared__ double s_key[kFindThreads];
+  __shared__ long long s_bg[kFindThreads], s_bh[kFindThreads];
+  __shared__ unsigned char s_usedf[kFindThreads], s_sorted[kFindThreads];
+  __shared__ Cand s_cand[8];
+  __shared__ int s_wused[8];
+  __shared__ unsigned int s_bits[8];
+  __shared__ CatDirBest s_dir[2];
+  __shared__ int s_pick_thr, s_pick_dir;
+  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
+  const int num_bin = fm.num_bin;
+  if (b < 8) s_bits[b] = 0u;
+  if (root) {      // leaf totals = sum of all bins of this feature
+    long long tg = g_in, th = h_in;
+    for (int o = 16; o > 0; o >>= 1) { tg += __shfl_xor_sync(0xffffffffu, tg, o); th += __shfl_xor_sync(0xffffffffu, th, o); }
+    if (lane == 0) { s_g[warp] = tg; s_h[warp] = th; }
+    SubSync(sub);
+    tot_g = 0; tot_h = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) { tot_g += s_g[w]; tot_h += s_h[w]; }
+    leaf_sum_g = static_cast<double>(tot_g) * gscale;
+    leaf_sum_h = static_cast<double>(tot_h) * hscale;
+    SubSync(sub);
+  }
+  *out_tot_g = tot_g; *out_tot_h = tot_h;
+  double sum_gradient, sum_hessian, cnt_factor;
+  if (QUANT) {
+    sum_gradient = static_cast<double>(tot_g) * gscale;
+    sum_hessian = static_cast<double>(tot_h) * hscale;
+    cnt_factor = static_cast<double>(num_data) / static_cast<double>(tot_h);
+  } else {
+    sum_gradient = leaf_sum_g;
+    sum_hessian = leaf_sum_h + 2 * KEPS;
+    cnt_factor = num_data / sum_hessian;
+  }
+  const double eps = QUANT ? 0.0 : KEPS;
+  const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
+  const double min_gain_shift = gain_shift + P.min_gain_to_split;
+  const bool valid = b >= 1 && b < num_bin && !(QUANT && tot_h <= 0);
+  const double grad = static_cast<double>(g_in) * gscale, hess = static_cast<double>(h_in) * hscale;
+  const int cnt = !valid ? 0 : QUANT ? RoundIntD(static_cast<double>(h_in) * cnt_factor) : RoundIntD(hess * cnt_factor);
+  const bool onehot = num_bin <= P.max_cat_to_onehot;
+  SplitDev s = EmptySplit(f, fm.real_index);
+  s.missing_type = fm.missing_type;
+  s.default_left = 0;
+  bool any = false;
+  if (onehot) {
+    Cand c; c.gain = KMINSCORE; c.b = -1; c.sg = 0; c.sh = 0; c.cnt = 0;
+    if (valid) {
+      bool ok = !(cnt < P.min_data_in_leaf || hess < P.min_sum_hessian) && !(num_data - cnt < P.min_data_in_leaf);
+      double soh, sog;
+      if (QUANT) { soh = static_cast<double>(tot_h - h_in) * hscale; sog = static_cast<double>(tot_g - g_in) * gscale; }
+      else { soh = sum_hessian - hess - KEPS; sog = sum_gradient - grad; }
+      ok = ok && !(soh < P.min_sum_hessian);
+      if (ok) {
+        const double gain = SplitGainD(sog, soh, grad, hess + eps, P);
+        if (gain > min_gain_shift) { c.gain = gain; c.b = b; c.sg = g_in; c.sh = h_in; c.cnt = cnt; }
+      }
+    }
+    const Cand best = BlockBestCand(c, false, s_cand, sub);
+    if (b == 0 && best.b >= 0) {
+      any = true;
+      const double blg = static_cast<double>(best.sg) * gscale, blh = static_cast<double>(best.sh) * hscale + eps;
+      s.left_count = best.cnt; s.right_count = num_data - best.cnt;
+      s.left_output = LeafOutputD(blg, blh, P);
+      if (QUANT) {
+        const long long rgi = tot_g - best.sg, rhi = tot_h - best.sh;
+        const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
+        s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = best.sg; s.left_int_h = best.sh;
+        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
+      } else {
+        s.left_sum_g = blg; s.left_sum_h = blh - KEPS;
+        s.right_output = LeafOutputD(sum_gradient - blg, sum_hessian - blh, P);
+        s.right_sum_g = sum_gradient - blg; s.right_sum_h = sum_hessian - blh - KEPS;
+      }
+      s.gain = best.gain - min_gain_shift;
+      s.cat_bits[best.b >> 5] = 1u << (best.b & 31);
+    }
+  } else {
+    LearnerParams Pc = P;
+    Pc.l2 += P.cat_l2;
+    const bool used = valid && static_cast<double>(cnt) >= P.cat_smooth;
+    const double key = grad / (hess + P.cat_smooth);
+    s_key[b] = key; s_bg[b] = g_in; s_bh[b] = h_in; s_usedf[b] = used ? 1 : 0;
+    const unsigned um = __ballot_sync(0xffffffffu, used);
+    if (lane == 0) s_wused[warp] = __popc(um);
+    SubSync(sub);
+    int used_bin = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) used_bin += s_wused[w];
+    if (used) {
+      int r = 0;
+      for (int j = 1; j < num_bin; ++j) {
+        const double kj = s_key[j];
+        if (s_usedf[j] && (kj < key || (kj == key && j < b))) ++r;
+      }
+      s_sorted[r] = static_cast<unsigned char>(b);
+    }
+    SubSync(sub);
+    if (b == 0 || b == 32) {
+      const int pass = b == 0 ? 0 : 1, dir = pass == 0 ? 1 : -1;
+      int start_pos = pass == 0 ? 0 : used_bin - 1;
+      const int max_num_cat = min(P.max_cat_threshold, (used_bin + 1) / 2);
+      CatDirBest best; best.gain = KMINSCORE; best.thr = -1; best.left_count = 0; best.ig = best.ih = 0; best.lg = best.lh = 0.0;
+      int cnt_cur_group = 0, left_count = 0;
+      double sum_left_gradient = 0.0, sum_left_hessian = KEPS;
+      long long ilg = 0, ilh = 0;
+      for (int i = 0; i < used_bin && i < max_num_cat; ++i) {
+        const int t = s_sorted[start_pos];
+        start_pos += dir;
+        const long long tg = s_bg[t], th = s_bh[t];
+        ilg += tg; ilh += th;
+        int c1;
+        if (QUANT) {
+          c1 = RoundIntD(static_cast<double>(th) * cnt_factor);
+          sum_left_gradient = static_cast<double>(ilg) * gscale;
+          sum_left_hessian = static_cast<double>(ilh) * hscale;
+        } else {
+          const double hb = static_cast<double>(th) * hscale;
+          c1 = RoundIntD(hb * cnt_factor);
+          sum_left_gradient += static_cast<double>(tg) * gscale;
+          sum_left_hessian += hb;
+        }
+        left_count += c1;
+        cnt_cur_group += c1;
+        if (left_count < P.min_data_in_leaf || sum_left_hessian < P.min_sum_hessian) continue;
+        const int right_count = num_data - left_count;
+        if (right_count < P.min_data_in_leaf || right_count < P.min_data_per_group) break;
+        const double sum_right_hessian = QUANT ? static_cast<double>(tot_h - ilh) * hscale : sum_hessian - sum_left_hessian;
+        if (sum_right_hessian < P.min_sum_hessian) break;
+        if (cnt_cur_group < P.min_data_per_group) continue;
+        cnt_cur_group = 0;
+        const double sum_right_gradient = QUANT ? static_cast<double>(tot_g - ilg) * gscale : sum_gradient - sum_left_gradient;
+        const double gain = SplitGainD(sum_left_gradient, sum_left_hessian, sum_right_gradient, sum_right_hessian, Pc);
+        if (gain <= min_gain_shift) continue;
+        if (gain > best.gain) {
+          best.gain = gain; best.thr = i; best.left_count = left_count; best.ig = ilg; best.ih = ilh;
+          best.lg = sum_left_gradient; best.lh = sum_left_hessian;
+        }
+      }
+      s_dir[pass] = best;
+    }
+    SubSync(sub);
+    if (b == 0) {
+      int dir = 1;
+      CatDirBest best = s_dir[0];
+      if (s_dir[1].thr >= 0 && (best.thr < 0 || s_dir[1].gain > best.gain)) { best = s_dir[1]; dir = -1; }
+      s_pick_thr = best.thr; s_pick_dir = dir;
+      if (best.thr >= 0) {
+        any = true;
+        s.left_count = best.left_count; s.right_count = num_data - best.left_count;
+        s.left_output = LeafOutputD(best.lg, best.lh, Pc);
+        if (QUANT) {
+          const long long rgi = tot_g - best.ig, rhi = tot_h - best.ih;
+          const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
+          s.left_sum_g = best.lg; s.left_sum_h = best.lh; s.left_int_g = best.ig; s.left_int_h = best.ih;
+          s.right_output = LeafOutputD(brg, brh, Pc);
+          s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
+        } else {
+          s.left_sum_g = best.lg; s.left_sum_h = best.lh - KEPS;
+          s.right_output = LeafOutputD(sum_gradient - best.lg, sum_hessian - best.lh, Pc);
+          s.right_sum_g = sum_gradient - best.lg; s.right_sum_h = sum_hessian - best.lh - KEPS;
+        }
+        s.gain = best.gain - min_gain_shift;
+      }
+    }
+    SubSync(sub);
+    const int thr = s_pick_thr;
+    if (b <= thr) {      // the categories of the chosen prefix
+      const int t = s_pick_dir == 1 ? s_sorted[b] : s_sorted[used_bin - 1 - b];
+      atomicOr(&s_bits[t >> 5], 1u << (t & 31));
+    }
+    SubSync(sub);
+    if (b == 0 && any) {
+      #pragma unroll
+      for (int i = 0; i < 8; ++i) s.cat_bits[i] = s_bits[i];
+    }
+  }
+  if (b == 0) {
+    s.is_cat = 1;
     *out = s;
     *splittable_out = any ? 1 : 0;
   }

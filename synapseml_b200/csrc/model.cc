@@ -51,11 +51,23 @@ void HostTree::AsConstantTree(double val) {
   leaf_value.assign(1, val);
 }
 
+bool HostTree::CategoricalGoesLeft(int node, double fval) const {
+  if (std::isnan(fval) || !(fval < 2147483648.0)) return false;
+  const int iv = static_cast<int>(fval);
+  if (iv < 0) return false;
+  const int k = static_cast<int>(threshold[node]);
+  const int words = cat_boundaries[k + 1] - cat_boundaries[k];
+  const int w = iv / 32;
+  if (w >= words) return false;
+  return (cat_threshold[cat_boundaries[k] + w] >> (iv % 32)) & 1u;
+}
+
 int HostTree::GetLeaf(const double* row) const {
   if (num_leaves <= 1) return 0;
   int node = 0;
   while (node >= 0) {
     double fval = row[split_feature[node]];
+    if (decision_type[node] & 1) { node = CategoricalGoesLeft(node, fval) ? left_child[node] : right_child[node]; continue; }
     const int mt = (decision_type[node] >> 2) & 3;
     const bool default_left = (decision_type[node] & 2) != 0;
     if (std::isnan(fval) && mt != 2) fval = 0.0;
@@ -72,7 +84,8 @@ std::string HostTree::ToString() const {
   auto fd = [](int8_t v) { return std::to_string(static_cast<int>(v)); };
   auto f17 = [](double v) { return G17(v); };
   auto fg = [](float v) { return Gs(v); };
-  std::string s = "num_leaves=" + std::to_string(num_leaves) + "\nnum_cat=0\n";
+  auto fu = [](uint32_t v) { return std::to_string(v); };
+  std::string s = "num_leaves=" + std::to_string(num_leaves) + "\nnum_cat=" + std::to_string(num_leaves > 1 ? num_cat : 0) + "\n";
   if (num_leaves > 1) {
     const int ni = num_leaves - 1;
     s += "split_feature=" + JoinN(split_feature, ni, fi) + "\n";
@@ -87,6 +100,10 @@ std::string HostTree::ToString() const {
     s += "internal_value=" + JoinN(internal_value, ni, f17) + "\n";
     s += "internal_weight=" + JoinN(internal_weight, ni, f17) + "\n";
     s += "internal_count=" + JoinN(internal_count, ni, fi) + "\n";
+    if (num_cat > 0) {
+      s += "cat_boundaries=" + JoinN(cat_boundaries, num_cat + 1, fi) + "\n";
+      s += "cat_threshold=" + JoinN(cat_threshold, static_cast<int>(cat_threshold.size()), fu) + "\n";
+    }
   } else {
     s += "leaf_value=" + G17(leaf_value[0]) + "\n";
   }
@@ -169,7 +186,8 @@ void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostT
     HostTree t;
     auto geti = [&](const char* k) { auto it = cur.find(k); if (it == cur.end()) throw std::runtime_error(std::string("Model string: tree block lacks '") + k + "'"); return atoi(it->second.c_str()); };
     t.num_leaves = geti("num_leaves");
-    if (cur.count("num_cat") && atoi(cur["num_cat"].c_str()) != 0) throw std::runtime_error("Model string: categorical splits are not supported by this library");
+    t.num_cat = cur.count("num_cat") ? atoi(cur["num_cat"].c_str()) : 0;
+    if (t.num_cat < 0) throw std::runtime_error("Model string: num_cat < 0");
     if (cur.count("is_linear") && atoi(cur["is_linear"].c_str()) != 0) throw std::runtime_error("Model string: linear trees are not supported by this library");
     if (t.num_leaves < 1) throw std::runtime_error("Model string: num_leaves < 1");
     auto toi = [](const std::string& x) { return atoi(x.c_str()); };
@@ -190,7 +208,17 @@ void ParseModelString(const std::string& text, ModelHeader* h, std::vector<HostT
       if (cur.count("internal_value")) ParseList(cur, "internal_value", ni, &t.internal_value, tod); else t.internal_value.assign(ni, 0.0);
       if (cur.count("internal_weight")) ParseList(cur, "internal_weight", ni, &t.internal_weight, tod); else t.internal_weight.assign(ni, 0.0);
       if (cur.count("internal_count")) ParseList(cur, "internal_count", ni, &t.internal_count, toi); else t.internal_count.assign(ni, 0);
+      if (t.num_cat > 0) {
+        auto tou = [](const std::string& x) { return static_cast<uint32_t>(strtoul(x.c_str(), nullptr, 10)); };
+        ParseList(cur, "cat_boundaries", static_cast<size_t>(t.num_cat) + 1, &t.cat_boundaries, toi);
+        if (t.cat_boundaries[0] != 0) throw std::runtime_error("Model string: cat_boundaries must start at 0");
+        for (int k = 0; k < t.num_cat; ++k)
+          if (t.cat_boundaries[k + 1] < t.cat_boundaries[k]) throw std::runtime_error("Model string: cat_boundaries must not decrease");
+        ParseList(cur, "cat_threshold", static_cast<size_t>(t.cat_boundaries[t.num_cat]), &t.cat_threshold, tou);
+      }
       for (size_t i = 0; i < ni; ++i) {
+        if ((t.decision_type[i] & 1) && !(t.threshold[i] >= 0 && t.threshold[i] < t.num_cat))
+          throw std::runtime_error("Model string: tree " + std::to_string(trees->size()) + " has a categorical node without a category set");
         const int l = t.left_child[i], r = t.right_child[i];
         auto ok = [&](int c) { return c >= 0 ? c < static_cast<int>(ni) : ~c < t.num_leaves; };
         if (!ok(l) || !ok(r) || t.split_feature[i] < 0 || t.split_feature[i] > h->max_feature_idx)
@@ -247,8 +275,18 @@ void NodeToJson(const HostTree& t, int index, std::string* s) {
     *s += "{\"split_index\":" + std::to_string(index) + ",\n";
     *s += "\"split_feature\":" + std::to_string(t.split_feature[index]) + ",\n";
     *s += "\"split_gain\":" + G17(AvoidInf(t.split_gain[index])) + ",\n";
-    *s += "\"threshold\":" + G17(AvoidInf(t.threshold[index])) + ",\n";
-    *s += "\"decision_type\":\"<=\",\n";
+    if (dt & 1) {      // Tree::NodeToJSON: the categories joined by "||", decision "=="
+      const int k = static_cast<int>(t.threshold[index]);
+      std::string cats;
+      for (int w = t.cat_boundaries[k]; w < t.cat_boundaries[k + 1]; ++w)
+        for (int j = 0; j < 32; ++j)
+          if ((t.cat_threshold[w] >> j) & 1u) { if (!cats.empty()) cats += "||"; cats += std::to_string((w - t.cat_boundaries[k]) * 32 + j); }
+      *s += "\"threshold\":\"" + cats + "\",\n";
+      *s += "\"decision_type\":\"==\",\n";
+    } else {
+      *s += "\"threshold\":" + G17(AvoidInf(t.threshold[index])) + ",\n";
+      *s += "\"decision_type\":\"<=\",\n";
+    }
     *s += std::string("\"default_left\":") + ((dt & 2) ? "true" : "false") + ",\n";
     *s += std::string("\"missing_type\":\"") + (mt == 0 ? "None" : mt == 1 ? "Zero" : "NaN") + "\",\n";
     *s += "\"internal_value\":" + G17(t.internal_value[index]) + ",\n";
@@ -292,7 +330,22 @@ std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees
   for (size_t j = 0; j < h.feature_infos.size() && j < h.feature_names.size(); ++j) {
     const std::string& fi = h.feature_infos[j];
     const size_t colon = fi.find(':');
-    if (fi.size() < 5 || fi[0] != '[' || colon == std::string::npos) continue;      // "none": a trivial feature
+    if (fi == "none" || colon == std::string::npos) continue;      // a trivial feature
+    if (fi[0] != '[') {      // categorical: the categories of its bins, "-1:3:1:..."
+      std::vector<long long> vals;
+      std::stringstream ss(fi);
+      std::string tok;
+      while (std::getline(ss, tok, ':')) if (!tok.empty()) vals.push_back(atoll(tok.c_str()));
+      if (vals.empty()) continue;
+      if (!first_obj) s += ",";
+      first_obj = false;
+      s += "\"" + JsonEscape(h.feature_names[j]) + "\":{\"min_value\":" + std::to_string(*std::min_element(vals.begin(), vals.end())) +
+           ",\"max_value\":" + std::to_string(*std::max_element(vals.begin(), vals.end())) + ",\"values\":[";
+      for (size_t k = 0; k < vals.size(); ++k) { if (k) s += ","; s += std::to_string(vals[k]); }
+      s += "]}";
+      continue;
+    }
+    if (fi.size() < 5) continue;
     if (!first_obj) s += ",";
     first_obj = false;
     s += "\"" + JsonEscape(h.feature_names[j]) + "\":{\"min_value\":" + fi.substr(1, colon - 1) + ",\"max_value\":" +
@@ -302,7 +355,7 @@ std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees
   for (int i = first; i < last; ++i) {
     const HostTree& t = trees[i];
     if (i > first) s += ",";
-    s += "{\"tree_index\":" + std::to_string(i) + ",\"num_leaves\":" + std::to_string(t.num_leaves) + ",\n\"num_cat\":0,\n";
+    s += "{\"tree_index\":" + std::to_string(i) + ",\"num_leaves\":" + std::to_string(t.num_leaves) + ",\n\"num_cat\":" + std::to_string(t.num_leaves > 1 ? t.num_cat : 0) + ",\n";
     s += "\"shrinkage\":" + G17(t.shrinkage) + ",\n\"tree_structure\":";
     if (t.num_leaves <= 1) s += "{\"leaf_value\":" + G17(t.leaf_value.empty() ? 0.0 : t.leaf_value[0]) + "}";
     else NodeToJson(t, 0, &s);

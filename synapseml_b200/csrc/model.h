@@ -17,6 +17,15 @@ struct HostTree {
   std::vector<int8_t> decision_type;
   std::vector<float> split_gain;
   std::vector<double> threshold, leaf_value, leaf_weight, internal_value, internal_weight;
+  // categorical splits (decision_type bit 0): node i of that kind keeps its index k among them in threshold[i]; its categories are
+  // the bits set in words [cat_boundaries[k], cat_boundaries[k + 1]) of cat_threshold (Tree::SplitCategorical, upstream tree.h).
+  // cat_bits_inner: for trees trained here, the same sets over BINS, 8 words per internal node (empty: no categorical split).
+  int num_cat = 0;
+  std::vector<int> cat_boundaries{0};
+  std::vector<uint32_t> cat_threshold;
+  std::vector<uint32_t> cat_bits_inner;
+  // Tree::CategoricalDecision: NaN, negative and unlisted values go right
+  bool CategoricalGoesLeft(int node, double fval) const;
 
   void Shrinkage(double rate);
   void AddBias(double val);
@@ -44,7 +53,7 @@ std::string ModelToString(const ModelHeader& h, const std::vector<HostTree>& tre
 std::string ModelToJson(const ModelHeader& h, const std::vector<HostTree>& trees, int start_iteration, int num_iteration,
                         const std::vector<double>& importance);
 
-// Inverse of ModelToString for the subset this library writes (no categorical splits, no linear trees):
+// Inverse of ModelToString for the subset this library writes (no linear trees):
 // what LGBM_BoosterLoadModelFromString reads when the Scala side rebuilds a booster from the model string on an executor
 // (lightgbm/src/main/scala/com/microsoft/azure/synapse/ml/lightgbm/booster/LightGBMBooster.scala:41-49).  Throws
 // std::runtime_error on malformed input.

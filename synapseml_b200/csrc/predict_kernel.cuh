@@ -26,7 +26,31 @@ struct PredModelDev {
   const int* left;
   const int* right;
   const double* leaf_value;
+  const int* cat_begin;              // categorical nodes (decision_type bit 0): the node's category set is words
+  const int* cat_words;              //   [cat_begin, cat_begin + cat_words) of cat_threshold, one bit per category value
+  const unsigned int* cat_threshold;
 };
+
+// Tree::Decision on a raw value.  Numerical: NaN counts as 0.0 unless the node's missing type is NaN; a missing value (zero for
+// missing type Zero, NaN for missing type NaN) follows default_left; everything else compares value <= threshold.  Categorical
+// (Tree::CategoricalDecision): the value is cut to an int; NaN, negative and unlisted values go right.
+__device__ __forceinline__ bool PredGoesLeft(const PredModelDev& m, int g, double fval) {
+  const double kZero = (double)1e-35f;
+  const int dt = m.decision_type[g];
+  if (dt & 1) {
+    if (fval != fval || !(fval < 2147483648.0)) return false;
+    const int iv = static_cast<int>(fval);
+    if (iv < 0) return false;
+    const int w = iv >> 5;
+    if (w >= m.cat_words[g]) return false;
+    return ((m.cat_threshold[m.cat_begin[g] + w] >> (iv & 31)) & 1u) != 0u;
+  }
+  const int mt = (dt >> 2) & 3;
+  const bool is_nan = fval != fval;
+  if (is_nan && mt != 2) fval = 0.0;
+  if ((mt == 1 && fval >= -kZero && fval <= kZero) || (mt == 2 && is_nan)) return (dt & 2) != 0;
+  return fval <= m.threshold[g];
+}
 
 constexpr int kPredictRaw = 1, kPredictNormal = 0, kPredictLeaf = 2, kPredictContrib = 3;
 
@@ -38,7 +62,6 @@ constexpr int kPredictRaw = 1, kPredictNormal = 0, kPredictLeaf = 2, kPredictCon
 template <typename T>
 __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long row_stride, long long col_stride, PredModelDev m, int t0,
                           int t1, int K, int average_over, int mode, int sigmoid_on, double sigmoid, double* __restrict__ out) {
-  const double kZero = (double)1e-35f;
   for (long long r = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; r < nrow; r += static_cast<long long>(gridDim.x) * blockDim.x) {
     const T* row = rows + r * row_stride;
     for (int cls = 0; cls < K; ++cls) {
@@ -50,15 +73,8 @@ __global__ void k_predict(const T* __restrict__ rows, long long nrow, long long 
           int node = 0;
           do {
             const int g = no + node;
-            double fval = static_cast<double>(row[static_cast<long long>(m.split_feature[g]) * col_stride]);
-            const int dt = m.decision_type[g];
-            const int mt = (dt >> 2) & 3;
-            const bool is_nan = fval != fval;
-            if (is_nan && mt != 2) fval = 0.0;
-            bool left;
-            if ((mt == 1 && fval >= -kZero && fval <= kZero) || (mt == 2 && is_nan)) left = (dt & 2) != 0;
-            else left = fval <= m.threshold[g];
-            node = left ? m.left[g] : m.right[g];
+            const double fval = static_cast<double>(row[static_cast<long long>(m.split_feature[g]) * col_stride]);
+            node = PredGoesLeft(m, g, fval) ? m.left[g] : m.right[g];
           } while (node >= 0);
           leaf = ~node;
         }
@@ -159,15 +175,7 @@ __device__ void TreeShapRecurse(const ShapCtx<T>& c, int node, int depth, ShapPa
   }
   const int g = c.no + node;
   const int feat = m.split_feature[g];
-  const double kZero = (double)1e-35f;
-  double fval = static_cast<double>(c.row[static_cast<long long>(feat) * c.col_stride]);
-  const int dt = m.decision_type[g];
-  const int mt = (dt >> 2) & 3;
-  const bool is_nan = fval != fval;
-  if (is_nan && mt != 2) fval = 0.0;
-  bool left;
-  if ((mt == 1 && fval >= -kZero && fval <= kZero) || (mt == 2 && is_nan)) left = (dt & 2) != 0;
-  else left = fval <= m.threshold[g];
+  const bool left = PredGoesLeft(m, g, static_cast<double>(c.row[static_cast<long long>(feat) * c.col_stride]));
   const int hot = left ? m.left[g] : m.right[g];
   const int cold = left ? m.right[g] : m.left[g];
   auto count = [&](int nd) { return static_cast<double>(nd >= 0 ? m.internal_count[c.no + nd] : m.leaf_count[c.lo + ~nd]); };

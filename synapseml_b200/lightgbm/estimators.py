@@ -70,6 +70,9 @@ _DEFAULTS = dict(
     labelCol="label", featuresCol="features", weightCol=None, initScoreCol=None, slotNames=None, referenceDataset=None,
     useQuantizedGrad=None, numGradQuantBins=None, stochasticRounding=None, isProvideTrainingMetric=None, delegate=None, validationIndicatorCol=None,
     defaultListenPort=nm.DEFAULT_LOCAL_LISTEN_PORT, timeout=1200.0, modelString=None,
+    # categorical features (LightGBMParams.scala:286-296, 451-483): slot indexes and / or slot names (resolved against slotNames)
+    categoricalSlotIndexes=None, categoricalSlotNames=None, minDataPerGroup=None, maxCatThreshold=None, catl2=None, catSmooth=None,
+    maxCatToOnehot=None,
     fobj=None,      # FObjTrait: an object with get_gradient(predictions [n][1], training_dataset) -> (grad f32[n], hess f32[n])
 )
 _SPARK_DEFAULTS = dict(maxBin=255, binSampleCount=200000, minDataInLeaf=20, numLeaves=31)   # values getXxx returns when unset
@@ -110,10 +113,26 @@ class LightGBMBase:
             return lambda: self._p[key] if self._p.get(key) is not None else _SPARK_DEFAULTS.get(key)
         raise AttributeError(name)
 
+    def get_categorical_indexes(self):
+        """LightGBMBase.scala:167-198 (getCategoricalIndexes): categoricalSlotNames looked up in slotNames (a name that is not there
+        resolves to -1 there too, which the native side then refuses), united with categoricalSlotIndexes.  (A LocalDataFrame carries
+        no ML attribute metadata, so nominal attributes cannot mark columns here.)"""
+        g = self._p
+        names = list(g["categoricalSlotNames"] or [])
+        slots = list(g["slotNames"] or [])
+        if names and not slots:
+            raise ValueError("categoricalSlotNames needs slotNames to resolve the names against")
+        by_name = [slots.index(n) if n in slots else -1 for n in names]
+        out = []
+        for i in list(g["categoricalSlotIndexes"] or []) + by_name:
+            if int(i) not in out:
+                out.append(int(i))
+        return out
+
     # ------------------------------------------------------------------ param groups (LightGBMBase.scala:240-372)
     def _general_params(self, num_tasks):
         g = self._p
-        return GeneralParams(parallelism=g["parallelism"], topK=g["topK"], numIterations=g["numIterations"], learningRate=g["learningRate"],
+        return GeneralParams(categoricalFeatures=self.get_categorical_indexes(), parallelism=g["parallelism"], topK=g["topK"], numIterations=g["numIterations"], learningRate=g["learningRate"],
                              numLeaves=g["numLeaves"], maxBin=g["maxBin"], binSampleCount=g["binSampleCount"],
                              baggingFraction=g["baggingFraction"], posBaggingFraction=g["posBaggingFraction"],
                              negBaggingFraction=g["negBaggingFraction"], baggingFreq=g["baggingFreq"], baggingSeed=g["baggingSeed"],
@@ -138,7 +157,7 @@ class LightGBMBase:
             objectiveParams=ObjectiveParams(g["objective"], g["fobj"]),
             seedParams=SeedParams(seed=g["seed"], deterministic=g["deterministic"], dataRandomSeed=g["dataRandomSeed"],
                                   boostingType=g["boostingType"], objective=g["objective"]),
-            categoricalParams=CategoricalParams(),
+            categoricalParams=CategoricalParams(g["minDataPerGroup"], g["maxCatThreshold"], g["catl2"], g["catSmooth"], g["maxCatToOnehot"]),
             quantizedParams=QuantizedGradParams(g["useQuantizedGrad"], g["numGradQuantBins"], g["stochasticRounding"]))
 
     def get_train_params(self, num_tasks, num_tasks_per_exec):
@@ -237,7 +256,7 @@ class LightGBMBase:
             total_rows = int(sum(counts))
         train_params = self.add_custom_train_params(self.get_train_params(world, num_tasks_per_exec), df, dist if dist_on else None)
         ds_params = dataset_creation_params(self.getMaxBin(), self.getBinSampleCount(), self.getMinDataInLeaf(),
-                                            train_params.executionParams.numThreads,
+                                            train_params.executionParams.numThreads, categorical_indexes=self.get_categorical_indexes(),
                                             data_random_seed=g["dataRandomSeed"] if g["dataRandomSeed"] is not None else g["seed"])
         if g["passThroughArgs"]:
             ds_params = g["passThroughArgs"] + " " + ds_params

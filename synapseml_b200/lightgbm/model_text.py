@@ -26,6 +26,11 @@ class TextTree:
             self.internal_value = f("internal_value", np.float64)
             self.internal_weight = f("internal_weight", np.float64)
             self.internal_count = f("internal_count", np.int64)
+            # categorical splits (decision_type bit 0): threshold = index k of the node's category set, words
+            # [cat_boundaries[k], cat_boundaries[k + 1]) of cat_threshold, one bit per category value
+            self.num_cat = int(kv.get("num_cat", 0))
+            self.cat_boundaries = f("cat_boundaries", np.int64)
+            self.cat_threshold = f("cat_threshold", np.uint64)
 
     def predict_leaf(self, X):
         n = X.shape[0]
@@ -43,6 +48,19 @@ class TextTree:
             fval = np.where(isnan & (mt != 2), 0.0, fval)
             is_missing = ((mt == 1) & (np.abs(fval) <= K_ZERO_THRESHOLD)) | ((mt == 2) & isnan)
             go_left = np.where(is_missing, default_left, fval <= self.threshold[nd])
+            is_cat = (self.decision_type[nd] & 1) != 0
+            if is_cat.any():      # Tree::CategoricalDecision: NaN, negative and unlisted values go right
+                raw = X[idx, self.split_feature[nd]]
+                ok = is_cat & ~np.isnan(raw) & (raw < 2147483648.0)
+                iv = np.where(ok, raw, 0.0).astype(np.int64)
+                ok &= iv >= 0
+                k = np.where(is_cat, self.threshold[nd], 0).astype(np.int64)
+                lo, hi = self.cat_boundaries[k], self.cat_boundaries[np.minimum(k + 1, len(self.cat_boundaries) - 1)]
+                w = iv >> 5
+                ok &= w < (hi - lo)
+                words = self.cat_threshold[np.where(ok, lo + w, 0)] if len(self.cat_threshold) else np.zeros(len(idx), dtype=np.uint64)
+                hit = ok & (((words >> (iv & 31).astype(np.uint64)) & np.uint64(1)) != 0)
+                go_left = np.where(is_cat, hit, go_left)
             nxt = np.where(go_left, self.left_child[nd], self.right_child[nd])
             node[idx] = nxt
             active[idx] = nxt >= 0
