@@ -28,21 +28,35 @@ def main():
     X, y = S.higgs_shape(hi - lo, start=lo)
     ok = True
     sampling = dict(baggingFraction=0.7, baggingFreq=1, featureFraction=0.7)      # every rank bags its own rows, all draw the same columns
-    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling))):
+    cats = dict(categoricalSlotIndexes=[2, 3], minDataPerGroup=50)      # two signal columns as 63 and 3 categories
+
+    def with_cats(A):
+        A = A.copy()
+        A[:, 2] = np.floor((A[:, 2] + np.pi) * 10.0)      # the label depends on sin(x2): not monotone in the category
+        return A                                          # (column 3 has three values already: one category against the rest)
+
+    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling), (True, cats))):
+        is_cat = "categoricalSlotIndexes" in extra
+        Xc = with_cats(X) if is_cat else X
         est = LightGBMClassifier(numIterations=iters, numLeaves=31, maxBin=63, useQuantizedGrad=quant, stochasticRounding=False,
                                  samplingMode="fixed", microBatchSize=8192, binSampleCount=50000,
                                  defaultListenPort=12400 + (os.getpid() % 1000) * 12 + case * 4, **extra)
-        model = est.fit(LocalDataFrame.from_arrays(X, y, num_partitions=2))
+        model = est.fit(LocalDataFrame.from_arrays(Xc, y, num_partitions=2))
         if rank == 0:
             from oracle import oracle as O
             Xa, ya = S.higgs_shape(n)
+            if is_cat:
+                Xa = with_cats(Xa)
             params = est.get_train_params(world, 2).to_string()
-            bst, _ = O.fit(Xa, ya, params, dataset_params="max_bin=63 bin_construct_sample_cnt=50000 min_data_in_leaf=20", n_shards=world,
-                           num_iterations=iters, sample_rows=50000)
+            dsp = "max_bin=63 bin_construct_sample_cnt=50000 min_data_in_leaf=20" + (" categorical_feature=2,3" if is_cat else "")
+            bst, _ = O.fit(Xa, ya, params, dataset_params=dsp, n_shards=world, num_iterations=iters, sample_rows=50000)
             ours, theirs = strip_parameters(model.model_str), strip_parameters(bst.save_model_to_string())
             if quant:
                 same = ours == theirs
-                print("quantized%s dp%d model identical to oracle: %s" % (" sampled" if extra else "", world, same), flush=True)
+                kind = " categorical" if is_cat else " sampled" if extra else ""
+                if is_cat:
+                    same = same and "num_cat=0" not in ours.split("Tree=1")[0]      # the first tree has categorical splits
+                print("quantized%s dp%d model identical to oracle: %s" % (kind, world, same), flush=True)
                 ok &= same
             else:
                 from synapseml_b200.lightgbm.model_text import TextModel
