@@ -141,8 +141,10 @@ int LGBM_NetworkFree(void);
 int LGBM_B200_DatasetGetFeatureInfo(DatasetHandle handle, int feature, int* num_bin, int* missing_type, int* default_bin,
                                     int* most_freq_bin, int* is_trivial, double* min_val, double* max_val);
 int LGBM_B200_DatasetGetBinUpperBounds(DatasetHandle handle, int feature, double* out);
-int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out);
+int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out);      /* non-trivial features */
+int LGBM_B200_DatasetGetNumColumns(DatasetHandle handle, int* out);         /* uint8 columns of the bin matrix (a feature with > 256 bins has several) */
 int LGBM_B200_DatasetCopyBinColumn(DatasetHandle handle, int inner_feature, uint8_t* out);
+int LGBM_B200_DatasetCopyBinColumn16(DatasetHandle handle, int inner_feature, uint16_t* out);   /* bins of the k-th non-trivial feature */
 int LGBM_B200_DatasetCopyRowMajor(DatasetHandle handle, int64_t row, int64_t nrows, int* out_stride, uint8_t* out);
 int LGBM_B200_BoosterGetGradients(BoosterHandle handle, float* grad, float* hess);
 int LGBM_B200_BoosterGetQuantGradients(BoosterHandle handle, int8_t* grad, int8_t* hess, double* scales);

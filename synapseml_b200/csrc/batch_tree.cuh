@@ -605,41 +605,55 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   const FeatureMetaDev fm = fmeta[f];
   const double gscale = ctrl->grad_scale, hscale = ctrl->hess_scale;
   const size_t slot_stride = static_cast<size_t>(F) * kBins * 2;
-  const size_t off = (static_cast<size_t>(f) * kBins + b) * 2;
-  longlong2 v;
   const size_t item_off = static_cast<size_t>(root ? 0 : k) * work_elems;
-  if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
-    long long a = 0, bsum = 0;
-    for (int r = 0; r < pt->world; ++r) {
-      const long long* w = pt->work[r] + pt->parity_off + item_off;
-      if (QUANT) a += w[static_cast<size_t>(f) * kBins + b];
-      else { const longlong2 t = *reinterpret_cast<const longlong2*>(w + off); a += t.x; bsum += t.y; }
+  // K5 for bin b of column `col`: this rank's (or all ranks') fresh sums, turned into the larger child's by subtracting them from
+  // the parent's, and stored in the child's pool slot
+  auto child_bin = [&](int col, bool store) -> longlong2 {
+    const size_t off = (static_cast<size_t>(col) * kBins + b) * 2;
+    longlong2 v;
+    if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
+      long long a = 0, bsum = 0;
+      for (int r = 0; r < pt->world; ++r) {
+        const long long* w = pt->work[r] + pt->parity_off + item_off;
+        if (QUANT) a += w[static_cast<size_t>(col) * kBins + b];
+        else { const longlong2 t = *reinterpret_cast<const longlong2*>(w + off); a += t.x; bsum += t.y; }
+      }
+      if (QUANT) { v.y = a & 0xffffffffLL; v.x = (a - v.y) >> 32; }
+      else { v.x = a; v.y = bsum; }
+    } else if (QUANT) {     // packed work area: (sum g << 32) + sum h
+      const long long pk = work[item_off + static_cast<size_t>(col) * kBins + b];
+      v.y = pk & 0xffffffffLL;
+      v.x = (pk - v.y) >> 32;
+    } else {
+      v = *reinterpret_cast<const longlong2*>(work + item_off + off);
     }
-    if (QUANT) { v.y = a & 0xffffffffLL; v.x = (a - v.y) >> 32; }
-    else { v.x = a; v.y = bsum; }
-  } else if (QUANT) {     // packed work area: (sum g << 32) + sum h
-    const long long pk = work[item_off + static_cast<size_t>(f) * kBins + b];
-    v.y = pk & 0xffffffffLL;
-    v.x = (pk - v.y) >> 32;
-  } else {
-    v = *reinterpret_cast<const longlong2*>(work + item_off + off);
-  }
-  bool used = true;
-  if (!root) {
-    used = splittable[static_cast<size_t>(parent) * F + f] != 0;
-    if (c == 1) {
+    if (!root && c == 1) {
       const longlong2 p = *reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(parent_slot) * slot_stride + off);
       v.x = p.x - v.x; v.y = p.y - v.y;
     }
-  }
-  *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
+    if (store) *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
+    return v;
+  };
+  // a wide feature (more than 256 bins: several columns, dataset.h) is handled whole by the unit of its first column; the units
+  // of its other columns have nothing to compute and report "no split"
+  longlong2 v = make_longlong2(0, 0);
+  if (fm.wide_cols == 0) v = child_bin(f, true);
+  const bool used = root || splittable[static_cast<size_t>(parent) * F + f] != 0;
   SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
   unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
   long long tg = me.int_g, th = me.int_h;
   // column sample of this tree (feature_fraction): a feature outside it has no split.  At the root it still runs the search,
   // because the leaf totals come out of it, and its result is discarded.
   const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
-  if (!used || (!sampled && !root)) {
+  if (fm.wide_cols < 0) {
+    if (root) WideRootTotals(child_bin, fmeta[f + fm.wide_cols], f + fm.wide_cols, &tg, &th, sub);
+    if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
+  } else if (fm.wide_cols > 0) {
+    // the columns' sums are needed by the children whatever happens to this feature here (K5 runs for every column)
+    BlockFindBestWide<QUANT>(child_bin, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                             fb + f, spl, &tg, &th, pool + static_cast<size_t>(me.hist_slot) * slot_stride, sub);
+    if ((!used || !sampled) && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
+  } else if (!used || (!sampled && !root)) {
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
     if (fm.bin_type != 0)
@@ -1460,6 +1474,7 @@ __global__ void __launch_bounds__(kApplyThreads) k_bt_apply_tree(const uint8_t* 
       const FeatureMetaDev fm = fmeta[f];
       // the bin whose rows follow default_left: the NaN bin, or the zero bin under zero_as_missing
       const unsigned nan_bin = (CAT && (dt & 1)) ? 511u
+                               : fm.wide_cols != 0 ? static_cast<unsigned>(fm.nan_local)      // a column of a wide feature (dataset.h)
                                : (fm.missing_type == kMissingNaN) ? static_cast<unsigned>(fm.num_bin - 1)
                                : (fm.missing_type == kMissingZero) ? static_cast<unsigned>(fm.default_bin) : 256u;
       uint2 nd;

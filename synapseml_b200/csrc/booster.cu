@@ -126,7 +126,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // remote load per rank each hide NVLink latency better than a lane with eight — C5 on 8 GPUs: 0.94 vs 2.1 ms per iteration)
   find_warp_ = static_cast<long long>(F_) * 2 * kMaxBatch > 148LL * 8 * 2 && !net_->active();
   if (const char* env = getenv("LGB_B200_FIND_WARP")) find_warp_ = atoi(env) != 0;
-  if (ds_->has_categorical) find_warp_ = false;      // the categorical search exists in the CTA form only
+  if (ds_->has_categorical || ds_->has_wide) find_warp_ = false;      // the categorical and the wide-feature search exist in the CTA form only
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -264,6 +264,7 @@ void Booster::SetupExchange() {
       const double all_to_all_bytes = static_cast<double>(lp_.quantized ? hist_elems / 2 : hist_elems) * sizeof(long long) * kMaxBatch * world;
       bool sliced = F_ >= world && all_to_all_bytes > 16.0 * 1024 * 1024;
       if (const char* env = getenv("LGB_B200_SLICED")) sliced = atoi(env) != 0 && F_ >= world;
+      if (ds_->has_wide) sliced = false;      // a wide feature's columns are searched by one unit: they must not straddle two ranks
       peers_.sliced = sliced ? 1 : 0;
       peers_.f_lo = sliced ? static_cast<int>(static_cast<long long>(F_) * peers_.rank / world) : 0;
       peers_.f_hi = sliced ? static_cast<int>(static_cast<long long>(F_) * (peers_.rank + 1) / world) : F_;
@@ -848,10 +849,13 @@ void Booster::NormalizeDart() {
 }
 
 void Booster::SampleFeaturesForTree() {
-  const int min_cnt = std::min(2, F_);
-  const int cnt = std::max(static_cast<int>(F_ * cfg_.feature_fraction + 0.5), min_cnt);
+  // ColSampler::ResetByTree draws over the used FEATURES; a wide feature's columns share its draw
+  const int NF = ds_->num_logical_features();
+  const int min_cnt = std::min(2, NF);
+  const int cnt = std::max(static_cast<int>(NF * cfg_.feature_fraction + 0.5), min_cnt);
   std::vector<unsigned char> mask(F_, 0);
-  for (int f : feature_rand_.Sample(F_, cnt)) mask[f] = 1;
+  for (int lf : feature_rand_.Sample(NF, cnt))
+    for (int c = 0; c < ds_->logical_num_cols[lf]; ++c) mask[ds_->logical_first_col[lf] + c] = 1;
   // pageable source: the runtime stages it before the call returns, so the vector may go out of scope
   LGB_CUDA(cudaMemcpyAsync(d_feature_mask_.p, mask.data(), F_, cudaMemcpyHostToDevice, stream_));
 }
@@ -1070,6 +1074,10 @@ bool Booster::FetchTree(HostTree* t) {
       ++t->num_cat;
       t->cat_boundaries.push_back(t->cat_boundaries.back() + static_cast<int>(bits.size()));
       t->cat_threshold.insert(t->cat_threshold.end(), bits.begin(), bits.end());
+    } else if (m.num_bin > kMaxBinsPerFeature) {
+      // a wide feature's split arrives in column form (column of the feature, byte threshold): back to the logical bin
+      const int c = inner - ds_->real_to_inner[ds_->used[inner]];
+      t->threshold[i] = m.upper[c * kWideLocalBins + t->threshold_in_bin[i] - 1];
     } else {
       t->threshold[i] = m.upper[t->threshold_in_bin[i]];   // RealThreshold
     }

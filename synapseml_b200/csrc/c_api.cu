@@ -365,10 +365,22 @@ int LGBM_B200_DatasetGetBinUpperBounds(DatasetHandle handle, int feature, double
   for (int i = 0; i < m.num_bin; ++i) out[i] = m.upper[i];
   API_END();
 }
-int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<Dataset*>(handle)->num_features(); API_END(); }
-int LGBM_B200_DatasetCopyBinColumn(DatasetHandle handle, int inner_feature, uint8_t* out) {
+int LGBM_B200_DatasetGetNumUsedFeature(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<Dataset*>(handle)->num_logical_features(); API_END(); }
+int LGBM_B200_DatasetGetNumColumns(DatasetHandle handle, int* out) { API_BEGIN(); *out = static_cast<Dataset*>(handle)->num_features(); API_END(); }
+int LGBM_B200_DatasetCopyBinColumn16(DatasetHandle handle, int inner_feature, uint16_t* out) {
   API_BEGIN();
   static_cast<Dataset*>(handle)->CopyBinColumn(inner_feature, out);
+  API_END();
+}
+int LGBM_B200_DatasetCopyBinColumn(DatasetHandle handle, int inner_feature, uint8_t* out) {
+  API_BEGIN();
+  auto ds = static_cast<Dataset*>(handle);
+  std::vector<uint16_t> tmp(std::max<int64_t>(ds->num_data, 1));
+  ds->CopyBinColumn(inner_feature, tmp.data());
+  for (int64_t i = 0; i < ds->num_data; ++i) {
+    LGB_CHECK(tmp[i] < 256, "feature has more than 256 bins: use LGBM_B200_DatasetCopyBinColumn16");
+    out[i] = static_cast<uint8_t>(tmp[i]);
+  }
   API_END();
 }
 int LGBM_B200_DatasetCopyRowMajor(DatasetHandle handle, int64_t row, int64_t nrows, int* out_stride, uint8_t* out) {

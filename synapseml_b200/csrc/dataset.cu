@@ -492,7 +492,8 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   m.max_val = dv[nd - 1];
   m.bin_type = cat ? 1 : 0;
   int is_trivial = num_bin <= 1;
-  if (!is_trivial && p.pre_filter && num_bin <= kMaxBinsPerFeature) {
+  const bool cat_overflow = cat && num_bin > kMaxBinsPerFeature;      // refused by the host
+  if (!is_trivial && p.pre_filter && !cat_overflow) {
     // NeedFilter: numerical — no cut leaves filter_cnt sample rows on both sides; categorical — with at most two bins, no bin
     // against the rest does (more bins are never filtered)
     bool need = true;
@@ -518,7 +519,7 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
   m.default_bin = 0;
   m.most_freq_bin = 0;
   m.sparse_rate = 1.0;
-  if (!is_trivial && num_bin <= kMaxBinsPerFeature) {
+  if (!is_trivial && !cat_overflow) {
     if (cat) { for (int i = 1; i < num_bin; ++i) if (out[i] == 0.0) m.default_bin = i; }      // the bin of category 0, if it has one
     else m.default_bin = K1ValueToBin(0.0, out, num_bin, missing_type);
     int arg = 0;
@@ -546,14 +547,17 @@ __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, 
 constexpr int K2_ROWS = 128;
 constexpr int K2_FT = 32;
 
-// CAT: the dataset has categorical features.  Such a feature's row of `bounds` holds its kept categories in ascending order and
-// `catbin` the bin of each (BinMapper::ValueToBin, categorical: the value is cut to an int; NaN, negative and unlisted values
-// are bin 0): the same lower-bound search finds the slot, an equality test and one byte load finish it.
+// CAT: the dataset has categorical or wide features.  A categorical feature's row of `bounds` holds its kept categories in
+// ascending order and `catbin` the bin of each (BinMapper::ValueToBin, categorical: the value is cut to an int; NaN, negative and
+// unlisted values are bin 0): the same lower-bound search finds the slot, an equality test and one byte load finish it.
+// A column of a wide feature (more than 256 bins, dataset.h) searches the feature's bounds in global memory (16 halvings) and
+// writes the byte that codes the logical bin for this column.
 template <bool CAT>
 __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ data, int nrow, int ncol, long long start_row,
                                                    const double* __restrict__ bounds, const FeatureMetaDev* __restrict__ fmeta,
                                                    int f_used, uint8_t* __restrict__ cm, long long n_pad,
-                                                   uint8_t* __restrict__ rm, int rm_stride, const uint8_t* __restrict__ catbin) {
+                                                   uint8_t* __restrict__ rm, int rm_stride, const uint8_t* __restrict__ catbin,
+                                                   const double* __restrict__ wide_bounds) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sb = reinterpret_cast<double*>(smem_raw);                                       // [256 bins][32 features]
   uint8_t* tile_rm = smem_raw + sizeof(double) * K2_FT * kMaxBinsPerFeature;              // [128 rows][32 features]
@@ -564,7 +568,7 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
   for (int i = threadIdx.x; i < K2_FT * kMaxBinsPerFeature; i += blockDim.x) {
     const int f = i >> 8, b = i & 255;      // consecutive threads read consecutive bins of one feature (coalesced)
     sb[b * K2_FT + f] = (f0 + f < f_used) ? bounds[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0.0;
-    if (CAT) scb[b * K2_FT + f] = (f0 + f < f_used) ? catbin[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0;
+    if (CAT) scb[b * K2_FT + f] = (f0 + f < f_used && catbin != nullptr) ? catbin[(long long)(f0 + f) * kMaxBinsPerFeature + b] : 0;
   }
   const int fi = f0 + lane;
   int num_bin = 1, missing_type = 0, real = 0;
@@ -572,6 +576,19 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
   if (fi < f_used) {
     num_bin = fmeta[fi].num_bin; missing_type = fmeta[fi].missing_type; real = fmeta[fi].real_index;
     if (CAT && fmeta[fi].bin_type != 0) { is_cat = true; num_bin -= 1; missing_type = kMissingNone; }      // search the num_bin - 1 categories
+  }
+  bool is_wide = false;
+  int wide_c = 0, wide_nb = 0, wide_miss = -1, wide_mt = 0;
+  const double* wb = nullptr;
+  if (CAT && fi < f_used && fmeta[fi].wide_cols != 0) {
+    const int wc = fmeta[fi].wide_cols;
+    wide_c = wc > 0 ? 0 : -wc;
+    const FeatureMetaDev first = fmeta[fi - wide_c];      // the feature's first column carries the logical description
+    is_wide = true;
+    wide_nb = first.num_bin; wide_mt = first.missing_type;
+    wide_miss = wide_mt == kMissingNaN ? wide_nb - 1 : wide_mt == kMissingZero ? first.default_bin : -1;
+    wb = wide_bounds + first.wide_off;
+    num_bin = 1; missing_type = kMissingNone;      // the shared-memory search below does nothing for this lane
   }
   __syncthreads();
   const long long first_blk = start_row / K2_ROWS;
@@ -620,6 +637,37 @@ __global__ void __launch_bounds__(256) k2_bin_rows(const double* __restrict__ da
       for (int k = 0; k < 16; ++k) {
         const bool hit = !((unlisted >> k) & 1u) && myb[lo_[k] * K2_FT] == val[k];
         lo_[k] = hit ? static_cast<int>(scb[lo_[k] * K2_FT + lane]) : 0;
+      }
+    }
+    if (CAT && is_wide) {      // BinMapper::ValueToBin over the feature's wide_nb bounds, then the byte of this column
+      int wl[16], wr[16];
+      #pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const long long row = r0 + warp * 16 + k;
+        const bool in = row >= start_row && row < start_row + nrow;
+        double v = in ? data[(row - start_row) * (long long)ncol + real] : 0.0;      // (val[k] was already cleaned of NaNs above)
+        wl[k] = 0; wr[k] = wide_mt == kMissingNaN ? wide_nb - 2 : wide_nb - 1;
+        if (v != v) {
+          if (wide_mt == kMissingNaN) { wl[k] = wr[k] = wide_nb - 1; }
+          else v = 0.0;
+        }
+        val[k] = v;
+      }
+      for (int step = 0; step < 16; ++step) {
+        #pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const int l = wl[k], r = wr[k];
+          const int m = (r + l - 1) >> 1;
+          const bool go = l < r;
+          const bool le = val[k] <= wb[go ? m : 0];
+          wr[k] = (go && le) ? m : r;
+          wl[k] = (go && !le) ? m + 1 : l;
+        }
+      }
+      #pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int logical = wl[k], home = logical / kWideLocalBins;
+        lo_[k] = home == wide_c ? logical % kWideLocalBins + 1 : logical == wide_miss ? kWideMissing : home > wide_c ? kWideAbove : kWideBelow;
       }
     }
     unsigned int w[4];
@@ -672,19 +720,31 @@ static BinLayout ChooseLayout(int f_used) {
 Dataset::~Dataset() { FreeSlots(); }
 
 void Dataset::FinishSchema() {
-  used.clear();
+  used.clear(); logical_used.clear(); logical_first_col.clear(); logical_num_cols.clear();
   real_to_inner.assign(num_total_features, -1);
   max_num_bin = 1;
+  has_wide = false;
+  std::vector<double> hwb;      // bounds of the wide features
+  std::vector<int> wide_off(num_total_features, 0);
   for (int j = 0; j < num_total_features; ++j) {
-    if (!mappers[j].is_trivial) {
-      real_to_inner[j] = static_cast<int>(used.size());
-      used.push_back(j);
-      max_num_bin = std::max(max_num_bin, mappers[j].num_bin);
+    const BinMapperH& m = mappers[j];
+    if (m.is_trivial) continue;
+    LGB_CHECK(m.num_bin <= kMaxWideBins, "Feature %d has %d bins; at most %d are supported", j, m.num_bin, kMaxWideBins);
+    LGB_CHECK(m.bin_type == 0 || m.num_bin <= kMaxBinsPerFeature, "Categorical feature %d has %d bins; at most %d are supported", j, m.num_bin,
+              kMaxBinsPerFeature);
+    const int cols = m.num_bin <= kMaxBinsPerFeature ? 1 : CeilDiv(m.num_bin, kWideLocalBins);
+    real_to_inner[j] = static_cast<int>(used.size());
+    logical_used.push_back(j);
+    logical_first_col.push_back(static_cast<int>(used.size()));
+    logical_num_cols.push_back(cols);
+    for (int c = 0; c < cols; ++c) used.push_back(j);
+    if (cols > 1) {
+      has_wide = true;
+      wide_off[j] = static_cast<int>(hwb.size());
+      hwb.insert(hwb.end(), m.upper.begin(), m.upper.end());
     }
+    max_num_bin = std::max(max_num_bin, cols > 1 ? kMaxBinsPerFeature : m.num_bin);
   }
-  LGB_CHECK(max_num_bin <= kMaxBinsPerFeature,
-            "A feature has %d bins; only uint8 bin storage (<= %d bins, max_bin <= 255) is built in this version",
-            max_num_bin, kMaxBinsPerFeature);
   if (feature_names.empty())
     for (int j = 0; j < num_total_features; ++j) feature_names.push_back("Column_" + std::to_string(j));
   const int F = num_features();
@@ -696,6 +756,17 @@ void Dataset::FinishSchema() {
   has_categorical = false;
   for (int i = 0; i < F; ++i) {
     const BinMapperH& m = mappers[used[i]];
+    const int first = real_to_inner[used[i]];
+    if (m.num_bin > kMaxBinsPerFeature) {      // a column of a wide feature: its bounds live in d_wide_bounds
+      const int S = CeilDiv(m.num_bin, kWideLocalBins), c = i - first;
+      // the bin whose rows follow default_left: the NaN bin, or the zero bin under zero_as_missing
+      const int miss = m.missing_type == kMissingNaN ? m.num_bin - 1 : m.missing_type == kMissingZero ? m.default_bin : -1;
+      const int nan_local = miss < 0 ? 256 : (miss / kWideLocalBins == c ? miss % kWideLocalBins + 1 : kWideMissing);
+      hm[i] = FeatureMetaDev{c == 0 ? m.num_bin : kMaxBinsPerFeature, m.missing_type, m.default_bin, m.most_freq_bin, used[i], 0,
+                             c == 0 ? S : -c, nan_local, wide_off[used[i]], 0};
+      hr[i] = used[i];
+      continue;
+    }
     if (m.bin_type != 0) {      // categorical: the kept categories in ascending order and the bin of each (the row-binning kernel's search)
       std::vector<std::pair<int, int>> cb;
       for (int b = 1; b < m.num_bin; ++b) cb.emplace_back(m.bin_2_cat[b], b);
@@ -708,7 +779,7 @@ void Dataset::FinishSchema() {
     } else {
       for (int b = 0; b < m.num_bin; ++b) hb[static_cast<size_t>(i) * kMaxBinsPerFeature + b] = m.upper[b];
     }
-    hm[i] = FeatureMetaDev{m.num_bin, m.missing_type, m.default_bin, m.most_freq_bin, used[i], m.bin_type, {0, 0}};
+    hm[i] = FeatureMetaDev{m.num_bin, m.missing_type, m.default_bin, m.most_freq_bin, used[i], m.bin_type, 0, 0, 0, 0};
     hr[i] = used[i];
   }
   LGB_CUDA(cudaSetDevice(device));
@@ -716,6 +787,10 @@ void Dataset::FinishSchema() {
   LGB_CUDA(cudaMemcpy(d_bounds.p, hb.data(), hb.size() * sizeof(double), cudaMemcpyHostToDevice));
   d_fmeta.Alloc(hm.size());
   LGB_CUDA(cudaMemcpy(d_fmeta.p, hm.data(), hm.size() * sizeof(FeatureMetaDev), cudaMemcpyHostToDevice));
+  if (has_wide) {
+    d_wide_bounds.Alloc(hwb.size());
+    LGB_CUDA(cudaMemcpy(d_wide_bounds.p, hwb.data(), hwb.size() * sizeof(double), cudaMemcpyHostToDevice));
+  }
   if (has_categorical) {
     d_catbin.Alloc(hcb.size());
     LGB_CUDA(cudaMemcpy(d_catbin.p, hcb.data(), hcb.size(), cudaMemcpyHostToDevice));
@@ -747,7 +822,7 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   g_verbosity = ds->cfg.verbosity;
   const Config& c = ds->cfg;
   LGB_CHECK(ncol > 0, "ncol must be positive");
-  LGB_CHECK(c.max_bin >= 2 && c.max_bin <= 255, "max_bin=%d is outside [2, 255] (uint8 bin storage)", c.max_bin);
+  LGB_CHECK(c.max_bin >= 2 && c.max_bin <= kMaxWideBins, "max_bin=%d is outside [2, %d]", c.max_bin, kMaxWideBins);
   std::vector<unsigned char> h_is_cat(ncol, 0);
   for (int j : c.categorical_feature) {
     LGB_CHECK(j >= 0 && j < ncol, "categorical_feature=%d is not a column index (0..%d)", j, ncol - 1);
@@ -823,8 +898,8 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
     m.default_bin = hmeta[j].default_bin; m.most_freq_bin = hmeta[j].most_freq_bin; m.sparse_rate = hmeta[j].sparse_rate;
     m.min_val = hmeta[j].min_val; m.max_val = hmeta[j].max_val;
     m.bin_type = hmeta[j].bin_type;
-    LGB_CHECK(m.num_bin <= kMaxBinsPerFeature,
-              "Categorical feature %d needs more than %d bins; only uint8 bin storage is built in this version", j, kMaxBinsPerFeature);
+    LGB_CHECK(m.bin_type == 0 || m.num_bin <= kMaxBinsPerFeature,
+              "Categorical feature %d needs more than %d bins, which is not supported", j, kMaxBinsPerFeature);
     m.upper.assign(hb.begin() + static_cast<size_t>(j) * p.bstride, hb.begin() + static_cast<size_t>(j) * p.bstride + m.num_bin);
     if (m.bin_type != 0) {      // the "bounds" of a categorical feature are the categories of its bins
       m.bin_2_cat.resize(m.num_bin);
@@ -999,19 +1074,20 @@ void Dataset::LaunchBinRows(const double* staged, int nrow, long long start_row,
   const long long nblk = (start_row + nrow - 1) / K2_ROWS - start_row / K2_ROWS + 1;
   const int ftiles = CeilDiv(F, K2_FT);
   dim3 grid(static_cast<unsigned>(std::min<long long>(nblk, std::max(1, 148 * 4 / ftiles))), ftiles);
-  const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS + (has_categorical ? K2_FT * kMaxBinsPerFeature : 0);
+  const bool ext = has_categorical || has_wide;
+  const size_t smem = sizeof(double) * K2_FT * kMaxBinsPerFeature + K2_FT * K2_ROWS + (ext ? K2_FT * kMaxBinsPerFeature : 0);
   static bool attr_set[2] = {false, false};
-  if (!attr_set[has_categorical ? 1 : 0]) {
-    if (has_categorical) LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if (!attr_set[ext ? 1 : 0]) {
+    if (ext) LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     else LGB_CUDA(cudaFuncSetAttribute(k2_bin_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    attr_set[has_categorical ? 1 : 0] = true;
+    attr_set[ext ? 1 : 0] = true;
   }
-  if (has_categorical)
+  if (ext)
     k2_bin_rows<true><<<grid, 256, smem, stream>>>(staged, nrow, num_total_features, start_row, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p,
-                                                   layout.rm_stride, d_catbin.p);
+                                                   layout.rm_stride, has_categorical ? d_catbin.p : nullptr, has_wide ? d_wide_bounds.p : nullptr);
   else
     k2_bin_rows<false><<<grid, 256, smem, stream>>>(staged, nrow, num_total_features, start_row, d_bounds.p, d_fmeta.p, F, d_cm.p, n_pad, d_rm.p,
-                                                    layout.rm_stride, nullptr);
+                                                    layout.rm_stride, nullptr, nullptr);
 }
 
 void Dataset::FlushSlot(PushSlot* s) {
@@ -1174,10 +1250,21 @@ void Dataset::MarkFinished() {
   finished = true;
 }
 
-void Dataset::CopyBinColumn(int inner_feature, uint8_t* out) const {
-  LGB_CHECK(inner_feature >= 0 && inner_feature < num_features(), "inner feature %d out of range", inner_feature);
+void Dataset::CopyBinColumn(int logical_feature, uint16_t* out) const {
+  LGB_CHECK(logical_feature >= 0 && logical_feature < num_logical_features(), "feature %d out of range", logical_feature);
   LGB_CUDA(cudaSetDevice(device));
-  LGB_CUDA(cudaMemcpy(out, d_cm.p + static_cast<size_t>(inner_feature) * n_pad, num_data, cudaMemcpyDeviceToHost));
+  const int first = logical_first_col[logical_feature], cols = logical_num_cols[logical_feature];
+  std::vector<uint8_t> col(num_data);
+  std::vector<int> seen(num_data, 0);
+  for (int c = 0; c < cols; ++c) {
+    LGB_CUDA(cudaMemcpy(col.data(), d_cm.p + static_cast<size_t>(first + c) * n_pad, num_data, cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < num_data; ++i) {
+      if (cols == 1) { out[i] = col[i]; continue; }
+      if (col[i] >= 1 && col[i] <= kWideLocalBins) { out[i] = static_cast<uint16_t>(c * kWideLocalBins + col[i] - 1); ++seen[i]; }
+    }
+  }
+  if (cols > 1)
+    for (int64_t i = 0; i < num_data; ++i) LGB_CHECK(seen[i] == 1, "row %lld of a wide feature is coded in %d columns", (long long)i, seen[i]);
 }
 
 void Dataset::CopyRowMajor(int64_t row, int64_t nrows, uint8_t* out) const {

@@ -21,7 +21,17 @@ namespace lgb {
 
 enum MissingType { kMissingNone = 0, kMissingZero = 1, kMissingNaN = 2 };
 
-constexpr int kMaxBinsPerFeature = 256;   // uint8 bin matrix (uint16 storage is not built yet; rejected loudly)
+constexpr int kMaxBinsPerFeature = 256;   // bins of one uint8 column of the bin matrix
+// A feature with more than 256 bins ("wide": max_bin > 255, what upstream stores as uint16) occupies S = ceil(num_bin / 253)
+// consecutive uint8 columns.  Column c holds the logical bins [253 c, 253 c + 253) as the bytes 1..253; a row whose bin lives in a
+// later column reads kWideAbove there, in an earlier column kWideBelow, and the rows of the feature's missing bin (NaN bin, or the
+// zero bin under zero_as_missing) read kWideMissing in every column but their own.  With that code the histogram, partition and
+// score kernels work on such a column unchanged: a split at logical bin t is the split (column t / 253, byte t % 253 + 1), where
+// "byte <= threshold" sends the rows below left and the rows above right, and the missing byte follows default_left.  Only the
+// row binning (writes S bytes per value) and the split search (scans the S columns as one feature) know about it.
+constexpr int kWideLocalBins = 253;
+constexpr int kWideBelow = 0, kWideMissing = 254, kWideAbove = 255;
+constexpr int kMaxWideBins = 65535;
 
 struct BinMapperH {
   int num_bin = 1;
@@ -44,7 +54,12 @@ struct FeatureMetaDev {
   int most_freq_bin;
   int real_index;
   int bin_type;        // 1: categorical
-  int pad_[2];
+  // wide features (more than 256 bins): wide_cols = S in the feature's first column (whose num_bin / default_bin / most_freq_bin
+  // are the LOGICAL ones), -k in its k-th further column, 0 for an ordinary feature; nan_local: the byte whose rows follow
+  // default_left in this column (the missing bin's own byte in its home column, kWideMissing elsewhere, 256 = no missing bin);
+  // wide_off: the feature's upper bounds in Dataset::d_wide_bounds
+  int wide_cols, nan_local, wide_off;
+  int pad_;
 };
 
 // HBM layout of the binned matrix.  Two copies are kept, both written by the K2 kernel in one pass:
@@ -65,8 +80,13 @@ class Dataset {
   int device = 0;
   int num_total_features = 0;
   std::vector<BinMapperH> mappers;       // per real feature
-  std::vector<int> used;                 // inner -> real
-  std::vector<int> real_to_inner;
+  std::vector<int> used;                 // inner column -> real feature (a wide feature has several consecutive columns)
+  std::vector<int> real_to_inner;        // real feature -> its first inner column (-1: trivial)
+  std::vector<int> logical_used;         // the non-trivial real features in order: what upstream calls the inner features
+  std::vector<int> logical_first_col, logical_num_cols;      // per logical feature
+  bool has_wide = false;
+  DevBuf<double> d_wide_bounds;          // upper bounds of the wide features, feature after feature
+  int num_logical_features() const { return static_cast<int>(logical_used.size()); }
   int max_num_bin = 1;
   int64_t num_data = 0;
   int64_t n_pad = 0;
@@ -114,7 +134,7 @@ class Dataset {
   int num_features() const { return static_cast<int>(used.size()); }
 
   // introspection for parity tests
-  void CopyBinColumn(int inner_feature, uint8_t* out) const;
+  void CopyBinColumn(int logical_feature, uint16_t* out) const;      // bins of the k-th non-trivial feature (wide features decoded)
   void CopyRowMajor(int64_t row, int64_t nrows, uint8_t* out) const;
 
  private:

@@ -836,6 +836,258 @@ __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMe
   }
 }
 
+// ------------------------------------------------------------------------------------------------ K5 + K6, wide features
+// A feature with more than 256 bins lives in S uint8 columns (dataset.h: column c codes the logical bins [253 c, 253 c + 253) as the
+// bytes 1..253).  One 256-thread CTA — the unit of the feature's first column — searches it whole: the same scans, candidates and
+// tie rules as BlockFindBest, over the logical bins, column after column with the prefix sums carried from one column to the next.
+//   pass A  K5 for every column (child_bin(col, true): load / subtract from the parent / store) and the sums the scans need;
+//   pass B  per column: block-wide inclusive scan + carry, one reverse and one forward candidate per thread, each thread keeping
+//           the better of its candidates (reverse: the later column on equal gain, forward: the earlier).
+// The result is handed on in column form: the split's column, the byte threshold in it and the byte whose rows follow
+// default_left there, so that the partition and score kernels need not know the feature is wide.
+template <bool QUANT, typename Load>
+__device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f, bool root, long long tot_g, long long tot_h,
+                                  double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P, double gscale,
+                                  double hscale, SplitDev* out, unsigned char* splittable_out, long long* out_tot_g,
+                                  long long* out_tot_h, const long long* slot, int sub) {
+  __shared__ long long s_g[8], s_h[8];
+  __shared__ int s_c[8];
+  __shared__ Cand s_cand[8];
+  __shared__ int s_flag;
+  __shared__ long long s_bin0[2];
+  __shared__ int s_bin0c;
+  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
+  const int S = fm.wide_cols, NB = fm.num_bin;
+  const bool zero_type = fm.missing_type == kMissingZero;
+  const bool two_scans = fm.missing_type == kMissingNaN || zero_type;
+  const int nan_bin = !two_scans ? -1 : zero_type ? fm.default_bin : NB - 1;      // the bin both scans leave out
+  const int fstart = (two_scans && zero_type && fm.most_freq_bin == 0) ? 1 : 0;
+  const bool in_col = b >= 1 && b <= kWideLocalBins;
+  if (b == 0) s_flag = 0;
+  if (b == 1) { s_bin0[0] = s_bin0[1] = 0; s_bin0c = 0; }      // thread 1 owns logical bin 0: it alone writes these
+  auto block_sum3 = [&](long long& x, long long& y, int& z) {
+    for (int o = 16; o > 0; o >>= 1) {
+      x += __shfl_xor_sync(0xffffffffu, x, o); y += __shfl_xor_sync(0xffffffffu, y, o); z += __shfl_xor_sync(0xffffffffu, z, o);
+    }
+    SubSync(sub);
+    if (lane == 0) { s_g[warp] = x; s_h[warp] = y; s_c[warp] = z; }
+    SubSync(sub);
+    x = 0; y = 0; z = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) { x += s_g[w]; y += s_h[w]; z += s_c[w]; }
+  };
+  // ---- pass A: K5 for all columns; sums over all bins (the root's totals) and over the scanned bins
+  long long ag = 0, ah = 0, ug = 0, uh = 0;
+  for (int c = 0; c < S; ++c) {
+    const longlong2 v = child_bin(f + c, true);
+    const int L = c * kWideLocalBins + b - 1;
+    if (in_col && L < NB) {
+      ag += v.x; ah += v.y;
+      if (L != nan_bin) {
+        ug += v.x; uh += v.y;
+        if (L == 0) { s_bin0[0] = v.x; s_bin0[1] = v.y; }
+      }
+    }
+  }
+  { int z = 0; block_sum3(ag, ah, z); }
+  if (root) {
+    tot_g = ag; tot_h = ah;
+    leaf_sum_g = static_cast<double>(tot_g) * gscale;
+    leaf_sum_h = static_cast<double>(tot_h) * hscale;
+  }
+  *out_tot_g = tot_g; *out_tot_h = tot_h;
+  double sum_gradient, sum_hessian, cnt_factor;
+  if (QUANT) {
+    sum_gradient = static_cast<double>(tot_g) * gscale;
+    sum_hessian = static_cast<double>(tot_h) * hscale;
+    cnt_factor = static_cast<double>(num_data) / static_cast<double>(tot_h);
+  } else {
+    sum_gradient = leaf_sum_g;
+    sum_hessian = leaf_sum_h + 2 * KEPS;
+    cnt_factor = num_data / sum_hessian;
+  }
+  // float mode: the counts are sums of per-bin rounded counts, so their total over the scanned bins needs a pass of its own
+  int uc = 0;
+  if (!QUANT) {
+    for (int c = 0; c < S; ++c) {
+      const int L = c * kWideLocalBins + b - 1;
+      if (in_col && L < NB && L != nan_bin) {
+        const long long hv = slot[(static_cast<size_t>(f + c) * kBins + b) * 2 + 1];
+        const int cv = RoundIntD(static_cast<double>(hv) * hscale * cnt_factor);
+        uc += cv;
+        if (L == 0) s_bin0c = cv;
+      }
+    }
+  }
+  block_sum3(ug, uh, uc);
+  const long long Tg = ug, Th = uh; const int Tc = uc;
+  const long long g0 = s_bin0[0], h0 = s_bin0[1]; const int c0 = s_bin0c;
+  const double gain_shift = LeafGainD(sum_gradient, sum_hessian, P);
+  const double min_gain_shift = gain_shift + P.min_gain_to_split;
+  const int top = NB - 1 - ((two_scans && !zero_type) ? 1 : 0);
+  bool splittable = false;
+  Cand cr; cr.gain = KMINSCORE; cr.b = -1; cr.sg = 0; cr.sh = 0; cr.cnt = 0;
+  Cand cf = cr;
+  long long Cg = 0, Ch = 0; int Cc = 0;      // sums of the scanned bins of the columns before this one
+  // ---- pass B
+  for (int c = 0; c < S; ++c) {
+    const int L = c * kWideLocalBins + b - 1;
+    const bool use = in_col && L < NB && L != nan_bin;
+    long long gv = 0, hv = 0; int cv = 0;
+    if (use) {
+      const longlong2 t = *reinterpret_cast<const longlong2*>(slot + (static_cast<size_t>(f + c) * kBins + b) * 2);
+      gv = t.x; hv = t.y;
+      if (!QUANT) cv = RoundIntD(static_cast<double>(hv) * hscale * cnt_factor);
+    }
+    long long pg = gv, ph = hv; int pc = cv;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const long long tg = __shfl_up_sync(0xffffffffu, pg, o);
+      const long long th = __shfl_up_sync(0xffffffffu, ph, o);
+      const int tc = __shfl_up_sync(0xffffffffu, pc, o);
+      if (lane >= o) { pg += tg; ph += th; pc += tc; }
+    }
+    SubSync(sub);
+    if (lane == 31) { s_g[warp] = pg; s_h[warp] = ph; s_c[warp] = pc; }
+    SubSync(sub);
+    long long colg = 0, colh = 0; int colc = 0;
+    #pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      if (w < warp) { pg += s_g[w]; ph += s_h[w]; pc += s_c[w]; }
+      colg += s_g[w]; colh += s_h[w]; colc += s_c[w];
+    }
+    pg += Cg; ph += Ch; pc += Cc;
+    // reverse scan candidate: right = bins [L, top], threshold = L - 1
+    if (use && L >= 1 && L <= top) {
+      const long long rgi = Tg - (pg - gv), rhi = Th - (ph - hv);
+      double gain = 0.0; int rc; bool ok = true;
+      if (QUANT) {
+        rc = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+        const double srh = static_cast<double>(rhi) * hscale;
+        const int lc = num_data - rc;
+        const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
+        const double slh = static_cast<double>(lhi) * hscale;
+        ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
+        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      } else {
+        rc = Tc - (pc - cv);
+        const double rh = KEPS + static_cast<double>(rhi) * hscale;
+        const int lc = num_data - rc;
+        const double lh = sum_hessian - rh;
+        ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
+        if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
+      }
+      if (ok && gain > min_gain_shift) {
+        splittable = true;
+        if (gain >= cr.gain) { cr.gain = gain; cr.b = L; cr.sg = rgi; cr.sh = rhi; cr.cnt = rc; }      // a later column: the larger bin
+      }
+    }
+    // forward scan candidate: left = bins [fstart, L], threshold = L
+    if (two_scans && use && L >= fstart && L <= NB - 2) {
+      const long long lgi = pg - (fstart ? g0 : 0), lhi = ph - (fstart ? h0 : 0);
+      double gain = 0.0; int lc; bool ok = true;
+      if (QUANT) {
+        lc = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        const double slh = static_cast<double>(lhi) * hscale;
+        const int rc = num_data - lc;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double srh = static_cast<double>(rhi) * hscale;
+        ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
+        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      } else {
+        lc = pc - (fstart ? c0 : 0);
+        const double lh = KEPS + static_cast<double>(lhi) * hscale;
+        const int rc = num_data - lc;
+        const double rh = sum_hessian - lh;
+        ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
+        if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
+      }
+      if (ok && gain > min_gain_shift) {
+        splittable = true;
+        if (gain > cf.gain) { cf.gain = gain; cf.b = L; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }        // an earlier column keeps an equal gain
+      }
+    }
+    Cg += colg; Ch += colh; Cc += colc;
+  }
+  if (splittable) s_flag = 1;
+  const Cand best_r = BlockBestCand(cr, true, s_cand, sub);
+  Cand best_f = cf;
+  if (two_scans) best_f = BlockBestCand(cf, false, s_cand, sub);
+  SubSync(sub);
+  if (b == 0) {
+    const bool any = s_flag != 0;
+    SplitDev s = EmptySplit(f, fm.real_index);
+    s.missing_type = fm.missing_type;
+    int thr = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      const Cand& c = pass == 0 ? best_r : best_f;
+      if (pass == 1 && !two_scans) break;
+      if (!(any && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      const bool reverse = pass == 0;
+      if (QUANT) {
+        const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
+        const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
+        const double blg = static_cast<double>(lgi) * gscale, blh = static_cast<double>(lhi) * hscale;
+        const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
+        s.left_output = LeafOutputD(blg, blh, P);
+        s.left_count = RoundIntD(static_cast<double>(lhi) * cnt_factor);
+        s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = lgi; s.left_int_h = lhi;
+        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_count = RoundIntD(static_cast<double>(rhi) * cnt_factor);
+        s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
+      } else {
+        double best_lg, best_lh; int left_count;
+        if (reverse) {
+          const double rg = static_cast<double>(c.sg) * gscale, rh = KEPS + static_cast<double>(c.sh) * hscale;
+          best_lg = sum_gradient - rg; best_lh = sum_hessian - rh; left_count = num_data - c.cnt;
+        } else {
+          best_lg = static_cast<double>(c.sg) * gscale; best_lh = KEPS + static_cast<double>(c.sh) * hscale; left_count = c.cnt;
+        }
+        s.left_output = LeafOutputD(best_lg, best_lh, P);
+        s.left_count = left_count;
+        s.left_sum_g = best_lg; s.left_sum_h = best_lh - KEPS;
+        s.right_output = LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P);
+        s.right_count = num_data - left_count;
+        s.right_sum_g = sum_gradient - best_lg; s.right_sum_h = sum_hessian - best_lh - KEPS;
+      }
+      thr = reverse ? c.b - 1 : c.b;
+      s.gain = c.gain - min_gain_shift;
+      s.default_left = reverse ? 1 : 0;
+    }
+    if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    // column form: the split's column, the byte threshold in it, and the byte whose rows follow default_left there
+    const int ct = thr / kWideLocalBins;
+    const int miss = fm.missing_type == kMissingNaN ? NB - 1 : zero_type ? fm.default_bin : -1;
+    s.feature = f + ct;
+    s.threshold = thr % kWideLocalBins + 1;
+    s.nan_bin = miss < 0 ? -1 : (miss / kWideLocalBins == ct ? miss % kWideLocalBins + 1 : kWideMissing);
+    *out = s;
+    *splittable_out = any ? 1 : 0;
+  }
+}
+
+// Leaf totals of the root seen from a further column of a wide feature (every unit of the root reports them): the sum over the
+// feature's bins, read without storing anything.
+template <typename Load>
+__device__ void WideRootTotals(Load child_bin, const FeatureMetaDev first, int f0, long long* out_tot_g, long long* out_tot_h, int sub) {
+  __shared__ long long s_g[8], s_h[8];
+  const int b = threadIdx.x & (kFindThreads - 1), lane = b & 31, warp = b >> 5;
+  long long ag = 0, ah = 0;
+  for (int c = 0; c < first.wide_cols; ++c) {
+    const longlong2 v = child_bin(f0 + c, false);
+    const int L = c * kWideLocalBins + b - 1;
+    if (b >= 1 && b <= kWideLocalBins && L < first.num_bin) { ag += v.x; ah += v.y; }
+  }
+  for (int o = 16; o > 0; o >>= 1) { ag += __shfl_xor_sync(0xffffffffu, ag, o); ah += __shfl_xor_sync(0xffffffffu, ah, o); }
+  SubSync(sub);
+  if (lane == 0) { s_g[warp] = ag; s_h[warp] = ah; }
+  SubSync(sub);
+  ag = 0; ah = 0;
+  #pragma unroll
+  for (int w = 0; w < 8; ++w) { ag += s_g[w]; ah += s_h[w]; }
+  *out_tot_g = ag; *out_tot_h = ah;
+}
+
 // ------------------------------------------------------------------------------------------------ K6 as a warp scan
 // One WARP searches one feature of one leaf: lane l owns bins [8 l, 8 l + 8) — eight 16-byte histogram entries, one coalesced
 // 4 KB read per warp — sums them, the lane totals are prefix-summed with shuffles, and every lane evaluates its eight thresholds

@@ -88,9 +88,9 @@ class NativeDataset:
         return nu.value
 
     def bin_column(self, j):
-        col = np.zeros(self.n, dtype=np.uint8)
-        validate(self.lib.LGBM_B200_DatasetCopyBinColumn(self.handle, j, col.ctypes.data_as(C.POINTER(C.c_uint8))))
-        return col
+        col = np.zeros(self.n, dtype=np.uint16)
+        validate(self.lib.LGBM_B200_DatasetCopyBinColumn16(self.handle, j, col.ctypes.data_as(C.POINTER(C.c_uint16))))
+        return col if col.max(initial=0) > 255 else col.astype(np.uint8)
 
     def row_major(self, row=0, nrows=None):
         nrows = self.n - row if nrows is None else nrows
