@@ -35,12 +35,15 @@ def main():
         A[:, 2] = np.floor((A[:, 2] + np.pi) * 10.0)      # the label depends on sin(x2): not monotone in the category
         return A                                          # (column 3 has three values already: one category against the rest)
 
-    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling), (True, cats))):
+    wide = dict(maxBin=1023)      # features with more than 256 bins: several uint8 columns each, searched as one feature
+    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling), (True, cats), (True, wide))):
         is_cat = "categoricalSlotIndexes" in extra
         Xc = with_cats(X) if is_cat else X
-        est = LightGBMClassifier(numIterations=iters, numLeaves=31, maxBin=63, useQuantizedGrad=quant, stochasticRounding=False,
+        kw = dict(maxBin=63)
+        kw.update(extra)
+        est = LightGBMClassifier(numIterations=iters, numLeaves=31, useQuantizedGrad=quant, stochasticRounding=False,
                                  samplingMode="fixed", microBatchSize=8192, binSampleCount=50000,
-                                 defaultListenPort=12400 + (os.getpid() % 1000) * 12 + case * 4, **extra)
+                                 defaultListenPort=12400 + (os.getpid() % 1000) * 12 + case * 4, **kw)
         model = est.fit(LocalDataFrame.from_arrays(Xc, y, num_partitions=2))
         if rank == 0:
             from oracle import oracle as O
@@ -48,12 +51,12 @@ def main():
             if is_cat:
                 Xa = with_cats(Xa)
             params = est.get_train_params(world, 2).to_string()
-            dsp = "max_bin=63 bin_construct_sample_cnt=50000 min_data_in_leaf=20" + (" categorical_feature=2,3" if is_cat else "")
+            dsp = "max_bin=%d bin_construct_sample_cnt=50000 min_data_in_leaf=20" % kw["maxBin"] + (" categorical_feature=2,3" if is_cat else "")
             bst, _ = O.fit(Xa, ya, params, dataset_params=dsp, n_shards=world, num_iterations=iters, sample_rows=50000)
             ours, theirs = strip_parameters(model.model_str), strip_parameters(bst.save_model_to_string())
             if quant:
                 same = ours == theirs
-                kind = " categorical" if is_cat else " sampled" if extra else ""
+                kind = " categorical" if is_cat else " wide" if "maxBin" in extra else " sampled" if extra else ""
                 if is_cat:
                     same = same and "num_cat=0" not in ours.split("Tree=1")[0]      # the first tree has categorical splits
                 print("quantized%s dp%d model identical to oracle: %s" % (kind, world, same), flush=True)
