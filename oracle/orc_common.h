@@ -182,7 +182,7 @@ struct Config {
   double alpha = 0.9, fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;
   double feature_fraction = 1.0;
   int feature_fraction_seed = 2;
-  double bagging_fraction = 1.0;
+  double bagging_fraction = 1.0, pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;
   int bagging_freq = 0, bagging_seed = 3;
   // boosting = dart / goss (upstream config.h defaults)
   double drop_rate = 0.1, skip_drop = 0.5, top_rate = 0.2, other_rate = 0.1;
@@ -197,6 +197,7 @@ struct Config {
   std::vector<int> eval_at;
   // categorical features (upstream config.h defaults): column indexes, and the knobs of the categorical split search
   std::vector<int> categorical_feature;
+  std::vector<int> max_bin_by_feature;
   int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
   double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // everything seen, canonical key -> value (first writer wins)
@@ -317,6 +318,7 @@ struct Config {
     getd("feature_fraction", &feature_fraction);
     geti("feature_fraction_seed", &feature_fraction_seed);
     getd("bagging_fraction", &bagging_fraction);
+    getd("pos_bagging_fraction", &pos_bagging_fraction); getd("neg_bagging_fraction", &neg_bagging_fraction);
     geti("bagging_freq", &bagging_freq);
     geti("bagging_seed", &bagging_seed);
     getd("drop_rate", &drop_rate); getd("skip_drop", &skip_drop); getd("top_rate", &top_rate); getd("other_rate", &other_rate);
@@ -334,6 +336,7 @@ struct Config {
     if (has("label_gain")) label_gain = ParseList<double>(kv["label_gain"]);
     if (has("eval_at")) eval_at = ParseList<int>(kv["eval_at"]);
     if (has("categorical_feature")) categorical_feature = ParseList<int>(kv["categorical_feature"]);
+    if (has("max_bin_by_feature")) max_bin_by_feature = ParseList<int>(kv["max_bin_by_feature"]);
     geti("max_cat_to_onehot", &max_cat_to_onehot); geti("max_cat_threshold", &max_cat_threshold); geti("min_data_per_group", &min_data_per_group);
     getd("cat_smooth", &cat_smooth); getd("cat_l2", &cat_l2);
     // objective aliases

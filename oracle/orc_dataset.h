@@ -55,7 +55,8 @@ struct Dataset {
     for (int j = 0; j < ncol; ++j) {
       std::vector<double> vals(sample_data[j], sample_data[j] + num_per_col[j]);
       const bool cat = std::find(c.categorical_feature.begin(), c.categorical_feature.end(), j) != c.categorical_feature.end();
-      ds->mappers[j].FindBin(vals.data(), num_per_col[j], static_cast<size_t>(num_sample_row), c.max_bin, c.min_data_in_bin,
+      const int max_bin = c.max_bin_by_feature.empty() ? c.max_bin : c.max_bin_by_feature.at(j);
+      ds->mappers[j].FindBin(vals.data(), num_per_col[j], static_cast<size_t>(num_sample_row), max_bin, c.min_data_in_bin,
                              filter_cnt, c.feature_pre_filter, c.use_missing, c.zero_as_missing, cat);
     }
     ds->FinishSchema();

@@ -452,7 +452,10 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA } obj = OBJ_L2;
+  bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA; }
+  std::vector<double> ova_label_weights, ova_suml;      // multiclassova: per class [neg, pos] label weights and the weighted positives
+  double ova_sumw = 0.0;
   bool RenewsLeaves() const { return obj == OBJ_L1 || obj == OBJ_QUANTILE || obj == OBJ_MAPE; }      // IsRenewTreeOutput
   std::vector<std::vector<label_t>> label_weight;      // mape: per shard, 1 / max(1, |label|) (* weight)
   enum Boost { BOOST_GBDT, BOOST_RF, BOOST_DART, BOOST_GOSS } boost = BOOST_GBDT;
@@ -490,7 +493,7 @@ class Booster {
   // column / row sampling
   Random feature_rand;
   std::vector<char> tree_mask;             // this tree's column sample (all ones when feature_fraction == 1)
-  bool bagging = false;
+  bool bagging = false, balanced_bagging = false;
 
   Booster(const std::vector<const Dataset*>& ds, const char* params) {
     cfg = ds[0]->config;     // dataset-time params (max_bin ...) first, booster string overrides
@@ -527,7 +530,14 @@ class Booster {
     drop_rand = Random(cfg.drop_seed);
     feature_rand = Random(cfg.feature_fraction_seed);
     tree_mask.assign(F, 1);
-    bagging = (cfg.bagging_freq > 0 && cfg.bagging_fraction < 1.0) || boost == BOOST_GOSS;
+    // ResetSampleConfig: balanced bagging needs a binary objective (NumPositiveData) with positive rows
+    balanced_bagging = cfg.bagging_freq > 0 && (cfg.pos_bagging_fraction < 1.0 || cfg.neg_bagging_fraction < 1.0) && cfg.objective == "binary";
+    if (balanced_bagging) {
+      bool any_pos = false;
+      for (auto d : ds) for (int64_t i = 0; i < d->num_data && !any_pos; ++i) any_pos = d->label[i] > 0;
+      balanced_bagging = any_pos;
+    }
+    bagging = (cfg.bagging_freq > 0 && (cfg.bagging_fraction < 1.0 || balanced_bagging)) || boost == BOOST_GOSS;
     if (boost == BOOST_RF && !(bagging || cfg.feature_fraction < 1.0))
       throw std::runtime_error("oracle: boosting=rf needs bagging (bagging_freq > 0, bagging_fraction < 1) or feature_fraction < 1");
     for (auto& sh : shards) {
@@ -551,7 +561,9 @@ class Booster {
       const data_size_t n = static_cast<data_size_t>(sh.ds->num_data);
       data_size_t left = 0, right = n;
       for (data_size_t i = 0; i < n; ++i) {
-        if (sh.bag_rands[i / 1024].NextFloat() < cfg.bagging_fraction) sh.bag_indices[left++] = i;
+        // BalancedBaggingHelper: positives and negatives of a binary problem are kept with their own fractions
+        const double fraction = !balanced_bagging ? cfg.bagging_fraction : sh.ds->label[i] > 0 ? cfg.pos_bagging_fraction : cfg.neg_bagging_fraction;
+        if (sh.bag_rands[i / 1024].NextFloat() < fraction) sh.bag_indices[left++] = i;
         else sh.bag_indices[--right] = i;
       }
       sh.bag_cnt = left;
@@ -647,7 +659,7 @@ class Booster {
   // ScoreUpdater::AddScore(tree, class): every row walks the tree over its bins
   void AddTreeToScores(const Tree& t, int k) {
     for (auto& sh : shards) {
-      std::vector<double>& sc = (obj == OBJ_MULTICLASS) ? sh.score_k[k] : sh.score;
+      std::vector<double>& sc = IsMulti() ? sh.score_k[k] : sh.score;
       const int64_t n = sh.ds->num_data;
 #pragma omp parallel for schedule(static)
       for (int64_t i = 0; i < n; ++i) sc[i] += t.leaf_value[LeafByBins(t, sh.ds, static_cast<data_size_t>(i))];
@@ -793,6 +805,40 @@ class Booster {
         sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
         if (sh.ds->has_init_score) throw std::runtime_error("oracle: multiclass init scores are not restated");
       }
+    } else if (cfg.objective == "multiclassova") {
+      // MulticlassOVA::Init: one BinaryLogloss per class, positive = "label == class" (upstream src/objective/multiclass_objective.hpp)
+      obj = OBJ_MULTICLASSOVA;
+      K = cfg.num_class;
+      if (K < 2) throw std::runtime_error("oracle: multiclassova needs num_class >= 2");
+      std::vector<double> cnt(K, 0.0);
+      double total = 0.0;
+      ova_suml.assign(K, 0.0);
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        for (int64_t i = 0; i < d->num_data; ++i) {
+          const int l = static_cast<int>(d->label[i]);
+          if (l < 0 || l >= K) throw std::runtime_error("oracle: multiclassova label outside [0, num_class)");
+          const double w = has_weights ? d->weight[i] : 1.0;
+          cnt[l] += 1.0; total += 1.0; ova_suml[l] += w; ova_sumw += w;
+        }
+      }
+      class_need_train.assign(K, 1);
+      ova_label_weights.assign(2 * K, 1.0);
+      for (int k = 0; k < K; ++k) {
+        const double pos = cnt[k], neg = total - cnt[k];
+        if (pos == 0 || neg == 0) class_need_train[k] = 0;
+        if (cfg.is_unbalance && pos > 0 && neg > 0) {
+          if (pos > neg) ova_label_weights[2 * k] = pos / neg; else ova_label_weights[2 * k + 1] = neg / pos;
+        }
+        ova_label_weights[2 * k + 1] *= cfg.scale_pos_weight;
+      }
+      for (auto& sh : shards) {
+        const size_t n = sh.score.size();
+        sh.score_k.assign(K, std::vector<double>(n, 0.0));
+        sh.grad_k.assign(K, std::vector<score_t>(n, 0.0f));
+        sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
+        if (sh.ds->has_init_score) throw std::runtime_error("oracle: multiclass init scores are not restated");
+      }
     } else if (cfg.objective == "custom" || cfg.objective == "none") {
       obj = OBJ_CUSTOM;      // no objective function: gradients come from the caller (TrainOneIter(grad, hess))
     } else if (cfg.objective == "lambdarank") {
@@ -853,6 +899,12 @@ class Booster {
   double BoostFromScore() const {
     double suml = 0.0, sumw = 0.0;
     if (obj == OBJ_MULTICLASS) return std::log(std::max<double>(kEpsilon, class_init_probs[cur_class]));
+    if (obj == OBJ_MULTICLASSOVA) {      // BinaryLogloss::BoostFromScore of the class's one-vs-rest problem
+      double pavg = ova_suml[cur_class] / ova_sumw;
+      pavg = std::min(pavg, 1.0 - kEpsilon);
+      pavg = std::max<double>(pavg, kEpsilon);
+      return std::log(pavg / (1.0f - pavg)) / cfg.sigmoid;
+    }
     if (obj == OBJ_BINARY) {
       for (auto& sh : shards) {
         const Dataset* d = sh.ds;
@@ -896,6 +948,31 @@ class Booster {
 
   void GetGradients() {
     if (obj == OBJ_MULTICLASS) { GetGradientsMulticlass(); return; }
+    if (obj == OBJ_MULTICLASSOVA) {      // MulticlassOVA::GetGradients: BinaryLogloss::GetGradients per class on its slice of the scores
+      const double sig = cfg.sigmoid;
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        const int64_t n = d->num_data;
+        for (int k = 0; k < K; ++k) {
+#pragma omp parallel for schedule(static)
+          for (int64_t i = 0; i < n; ++i) {
+            const int is_pos = static_cast<int>(d->label[i]) == k;
+            const int label = is_pos ? 1 : -1;
+            const double lw = ova_label_weights[2 * k + is_pos];
+            const double response = -label * sig / (1.0f + SoftExp(label * sig * sh.score_k[k][i]));
+            const double abs_response = std::fabs(response);
+            if (!has_weights) {
+              sh.grad_k[k][i] = static_cast<score_t>(response * lw);
+              sh.hess_k[k][i] = static_cast<score_t>(abs_response * (sig - abs_response) * lw);
+            } else {
+              sh.grad_k[k][i] = static_cast<score_t>(response * lw * d->weight[i]);
+              sh.hess_k[k][i] = static_cast<score_t>(abs_response * (sig - abs_response) * lw * d->weight[i]);
+            }
+          }
+        }
+      }
+      return;
+    }
     for (int s = 0; s < S; ++s) {
       Shard& sh = shards[s];
       const Dataset* d = sh.ds;
@@ -1333,7 +1410,7 @@ class Booster {
   // automatic initial score and the objective's own gradients are not computed
   bool TrainOneIter(const float* custom_grad = nullptr, const float* custom_hess = nullptr) {
     const bool custom = custom_grad != nullptr;
-    const bool multi = obj == OBJ_MULTICLASS;
+    const bool multi = IsMulti();
     if (obj == OBJ_CUSTOM && !custom) throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
     if (multi && custom) throw std::runtime_error("oracle: caller-supplied gradients with multiclass are not restated");
     // multiclass: class k's scores / gradients take the place of the single-class arrays while its tree is handled
@@ -1431,7 +1508,7 @@ class Booster {
   // them on its own bag, carries the initial score as a bias, and the scores hold the running average of the trees.
   template <typename EnterFn, typename LeaveFn, typename InitFn>
   bool TrainOneIterRF(EnterFn enter_class, LeaveFn leave_class, InitFn automatic_init_score) {
-    const bool multi = obj == OBJ_MULTICLASS;
+    const bool multi = IsMulti();
     if (iter == 0 && rf_init_scores.empty()) {      // RF::Boosting
       rf_init_scores.assign(K, 0.0);
       for (int k = 0; k < K; ++k) {
@@ -1514,6 +1591,7 @@ class Booster {
     if (obj == OBJ_L2) return "regression";
     if (obj == OBJ_CUSTOM) return "";
     if (obj == OBJ_MULTICLASS) return "multiclass num_class:" + std::to_string(K);
+    if (obj == OBJ_MULTICLASSOVA) return "multiclassova num_class:" + std::to_string(K) + " sigmoid:" + FmtG(cfg.sigmoid);
     if (RenewsLeaves()) return cfg.objective;
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";

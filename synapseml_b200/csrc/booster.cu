@@ -75,9 +75,13 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // parameters that would change the model and are not implemented are refused rather than ignored
   LGB_CHECK(cfg_.feature_fraction_bynode == 1.0, "feature_fraction_bynode < 1 is not supported by this library yet");
   LGB_CHECK(cfg_.bagging_fraction > 0.0 && cfg_.bagging_fraction <= 1.0, "bagging_fraction=%g is outside (0, 1]", cfg_.bagging_fraction);
-  LGB_CHECK(!(cfg_.bagging_freq > 0 && (cfg_.pos_bagging_fraction < 1.0 || cfg_.neg_bagging_fraction < 1.0)),
-            "balanced bagging (pos_bagging_fraction / neg_bagging_fraction < 1) is not supported by this library yet");
-  for (const char* key : {"monotone_constraints", "max_bin_by_feature", "interaction_constraints", "forcedsplits_filename",
+  LGB_CHECK(cfg_.pos_bagging_fraction > 0.0 && cfg_.pos_bagging_fraction <= 1.0 && cfg_.neg_bagging_fraction > 0.0 && cfg_.neg_bagging_fraction <= 1.0,
+            "pos_bagging_fraction / neg_bagging_fraction must be in (0, 1]");
+  // (max_bin_by_feature belongs to dataset construction: given to the booster only, upstream warns that it cannot change a
+  // constructed dataset and goes on, which is what the reference's flow does — LightGBMBase.scala:374-386 never sends it there)
+  if (cfg_.raw.count("max_bin_by_feature") && train->cfg.max_bin_by_feature.empty())
+    LogWarning("Cannot change max_bin_by_feature after constructed Dataset handle.");
+  for (const char* key : {"monotone_constraints", "interaction_constraints", "forcedsplits_filename",
                           "cegb_penalty_split", "linear_tree", "extra_trees", "path_smooth", "feature_contri"}) {
     auto it = cfg_.raw.find(key);
     if (it == cfg_.raw.end()) continue;
@@ -182,7 +186,10 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     LGB_CUDA(cudaMemcpy(d_ctrl_, &hc, sizeof(hc), cudaMemcpyHostToDevice));
     if (const char* from = getenv("LGB_B200_TRACE_FROM")) trace_from_ = atoi(from);
   }
-  bagging_ = (cfg_.bagging_freq > 0 && cfg_.bagging_fraction < 1.0) || boost_ == kGOSS;
+  // ResetSampleConfig: balanced bagging (pos / neg_bagging_fraction) needs a binary objective with positive rows on this machine
+  balanced_bagging_ = cfg_.bagging_freq > 0 && (cfg_.pos_bagging_fraction < 1.0 || cfg_.neg_bagging_fraction < 1.0) && obj_ == kBinary &&
+                      std::any_of(ds_->label.begin(), ds_->label.end(), [](float l) { return l > 0; });
+  bagging_ = (cfg_.bagging_freq > 0 && (cfg_.bagging_fraction < 1.0 || balanced_bagging_)) || boost_ == kGOSS;
   if (bagging_) {      // ResetSampleConfig: one LCG stream per block of 1024 local rows, seeded bagging_seed + block
     const int nblk = static_cast<int>((n_ + 1023) / 1024);
     std::vector<unsigned int> seeds(nblk);
@@ -497,10 +504,39 @@ void Booster::InitObjective() {
       class_init_probs_[k] = acc[k] / acc[K_];
       if (std::fabs(class_init_probs_[k]) <= kEpsD || std::fabs(class_init_probs_[k]) >= 1.0 - kEpsD) class_need_train_[k] = 0;
     }
+  } else if (cfg_.objective == "multiclassova") {
+    // MulticlassOVA::Init: one BinaryLogloss per class whose positives are the rows of that class (label counts, is_unbalance /
+    // scale_pos_weight weights and the sums behind BoostFromScore, all over all machines)
+    obj_ = kMulticlassOva;
+    K_ = cfg_.num_class;
+    LGB_CHECK(K_ >= 2 && K_ <= kMaxClasses, "objective=multiclassova needs 2 <= num_class <= %d (got %d)", kMaxClasses, K_);
+    std::vector<double> acc(2 * K_ + 2, 0.0);      // [k]: rows of class k, [K + k]: their weight, [2K]: rows, [2K + 1]: weight
+    const std::vector<float>& wv = ds_->weight;
+    for (int64_t i = 0; i < n_; ++i) {
+      const int l = static_cast<int>(label[i]);
+      LGB_CHECK(l >= 0 && l < K_ && label[i] == static_cast<float>(l), "multiclassova labels must be integers in [0, %d)", K_);
+      const double w = has_weights_ ? wv[i] : 1.0;
+      acc[l] += 1.0; acc[K_ + l] += w; acc[2 * K_] += 1.0; acc[2 * K_ + 1] += w;
+    }
+    net_->HostAllReduceSum(acc.data(), 2 * K_ + 2);
+    class_need_train_.assign(K_, 1);
+    ova_label_weights_.assign(2 * K_, 1.0);
+    ova_suml_.assign(K_, 0.0);
+    ova_sumw_ = acc[2 * K_ + 1];
+    for (int k = 0; k < K_; ++k) {
+      const double pos = acc[k], neg = acc[2 * K_] - acc[k];
+      if (pos == 0 || neg == 0) class_need_train_[k] = 0;
+      if (cfg_.is_unbalance && pos > 0 && neg > 0) {
+        if (pos > neg) ova_label_weights_[2 * k] = pos / neg;
+        else ova_label_weights_[2 * k + 1] = neg / pos;
+      }
+      ova_label_weights_[2 * k + 1] *= cfg_.scale_pos_weight;
+      ova_suml_[k] = acc[K_ + k];
+    }
   } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
     obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, multiclassova, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
   }
 }
 
@@ -526,6 +562,12 @@ void Booster::ComputeGradients(const double* score_override) {
   const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
   if (obj_ == kMulticlass) {
     k_grad_multiclass<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[0].p, d_hess_[0].p, n, K_, static_cast<double>(K_) / (K_ - 1.0f));
+  } else if (obj_ == kMulticlassOva) {
+    for (int k = 0; k < K_; ++k)
+      k_grad_binary<<<grid, 256, 0, stream_>>>(score + static_cast<size_t>(k) * n_, ds_->d_label.p, w, d_grad_[0].p + static_cast<size_t>(k) * n_,
+                                               d_hess_[0].p + static_cast<size_t>(k) * n_, n, cfg_.sigmoid, ova_label_weights_[2 * k],
+                                               ova_label_weights_[2 * k + 1], k);
+    launches_ += K_ - 1;
   } else if (obj_ == kBinary) {
     k_grad_binary<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
@@ -708,7 +750,11 @@ void Booster::Bagging() {
   if (!bagging_ || iter_ % cfg_.bagging_freq != 0) return;
   const int n = static_cast<int>(n_);
   LGB_CUDA(cudaMemsetAsync(d_bag_count_.p, 0, sizeof(int), stream_));
-  k_bag_sample<<<CeilDiv(CeilDiv(n, 1024), 64), 64, 0, stream_>>>(d_bag_rand_.p, n, cfg_.bagging_fraction, d_bag_bits_.p, d_bag_count_.p);
+  if (balanced_bagging_)
+    k_bag_sample<<<CeilDiv(CeilDiv(n, 1024), 64), 64, 0, stream_>>>(d_bag_rand_.p, n, cfg_.neg_bagging_fraction, d_bag_bits_.p, d_bag_count_.p,
+                                                                    ds_->d_label.p, cfg_.pos_bagging_fraction);
+  else
+    k_bag_sample<<<CeilDiv(CeilDiv(n, 1024), 64), 64, 0, stream_>>>(d_bag_rand_.p, n, cfg_.bagging_fraction, d_bag_bits_.p, d_bag_count_.p);
   LGB_CUDA(cudaGetLastError());
   ++launches_;
   int local = 0;
@@ -1170,6 +1216,11 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
     double v;
     if (obj_ == kMulticlass) {
       v = std::log(std::max<double>(kEps, class_init_probs_[cls_]));
+    } else if (obj_ == kMulticlassOva) {      // BinaryLogloss::BoostFromScore of the class's one-vs-rest problem
+      double pavg = ova_suml_[cls_] / ova_sumw_;
+      pavg = std::min(pavg, 1.0 - kEps);
+      pavg = std::max<double>(pavg, kEps);
+      v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
     } else if (RenewsLeaves()) {
       // the (weighted) percentile of this machine's labels; ObtainAutomaticInitialScore then takes the mean over machines
       double acc = PercentileInitScore();
@@ -1324,6 +1375,10 @@ ModelHeader Booster::MakeHeader() const {
   if (obj_ == kBinary) h.objective = "binary sigmoid:" + FormatG(cfg_.sigmoid);
   else if (obj_ == kL2) h.objective = "regression";
   else if (obj_ == kMulticlass) { h.objective = "multiclass num_class:" + std::to_string(K_); h.num_class = K_; h.num_tree_per_iteration = K_; }
+  else if (obj_ == kMulticlassOva) {
+    h.objective = "multiclassova num_class:" + std::to_string(K_) + " sigmoid:" + FormatG(cfg_.sigmoid);
+    h.num_class = K_; h.num_tree_per_iteration = K_;
+  }
   else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie / regression_l1 / quantile / mape: the name alone
   else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
   else h.objective = "lambdarank";
@@ -1382,7 +1437,13 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
   } else if (o.rfind("lambdarank", 0) == 0) {
     obj_ = kLambdarank;
-  } else if (o.rfind("multiclass", 0) == 0 && o.rfind("multiclassova", 0) != 0) {
+  } else if (o.rfind("multiclassova", 0) == 0) {
+    obj_ = kMulticlassOva;
+    K_ = loaded_header_.num_tree_per_iteration;
+    LGB_CHECK(K_ >= 2 && K_ == loaded_header_.num_class, "Model string: multiclassova needs num_tree_per_iteration == num_class >= 2");
+    const size_t p = o.find("sigmoid:");
+    if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
+  } else if (o.rfind("multiclass", 0) == 0) {
     obj_ = kMulticlass;
     K_ = loaded_header_.num_tree_per_iteration;
     LGB_CHECK(K_ >= 2 && K_ == loaded_header_.num_class, "Model string: multiclass needs num_tree_per_iteration == num_class >= 2");
@@ -1551,7 +1612,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
   dp_in_.Reserve(static_cast<size_t>(chunk_rows) * ncol * esz);
   dp_out_.Reserve(static_cast<size_t>(chunk_rows) * per_row);
-  const int sig_on = obj_ == kBinary ? 1 : LogLink() ? 2 : obj_ == kMulticlass ? 3 : 0;      // ConvertOutput: sigmoid, exp, softmax or none
+  const int sig_on = (obj_ == kBinary || obj_ == kMulticlassOva) ? 1 : LogLink() ? 2 : obj_ == kMulticlass ? 3 : 0;      // ConvertOutput: sigmoid, exp, softmax or none
   for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
     const int64_t nr = std::min(chunk_rows, nrow - r0);
     const unsigned char* src = static_cast<const unsigned char*>(data) + (row_major ? static_cast<size_t>(r0) * ncol * esz : 0);

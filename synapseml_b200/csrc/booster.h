@@ -178,10 +178,14 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass, kL1, kQuantile, kMape } obj_ = kL2;
+  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass, kL1, kQuantile, kMape, kMulticlassOva } obj_ = kL2;
   bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie) || RenewsLeaves(); }
   // l1 / quantile / mape (upstream IsRenewTreeOutput): every leaf's output is re-fit as a percentile of the residuals of its rows
   bool RenewsLeaves() const { return obj_ == kL1 || obj_ == kQuantile || obj_ == kMape; }
+  // multiclassova (upstream MulticlassOVA: one BinaryLogloss per class, positive = "label == class"): per class the label
+  // weights [neg, pos] and the (weighted) sums behind BoostFromScore, over all machines
+  std::vector<double> ova_label_weights_, ova_suml_;
+  double ova_sumw_ = 0.0;
   void RenewTreeOutput(HostTree* tree);
   double PercentileInitScore() const;
   std::vector<float> label_weight_;          // mape: 1 / max(1, |label|) [* weight]
@@ -278,6 +282,7 @@ class Booster {
   bool TrainOneIter(const float* grad, const float* hess);
   // bagging (bagging_freq > 0, bagging_fraction < 1): the bag as a bit per row, re-drawn every bagging_freq iterations
   bool bagging_ = false;
+  bool balanced_bagging_ = false;      // pos_bagging_fraction / neg_bagging_fraction (binary objective)
   DevBuf<unsigned int> d_bag_bits_, d_bag_rand_;
   DevBuf<int> d_bag_count_;
   long long bag_cnt_global_ = 0;

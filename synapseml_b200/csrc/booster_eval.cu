@@ -18,7 +18,7 @@ namespace lgb {
 namespace {
 constexpr int kNumSms = 148;
 enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
-       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15 };   // (Booster has its own kL2: distinct names)
+       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15, kEvGammaDeviance = 16 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -38,7 +38,7 @@ void Booster::InitMetrics() {
     }
   }
   if (names.empty() && obj_ != kCustom)      // the objective's default; a custom objective has none
-    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : obj_ == kMulticlass ? "multi_logloss"
+    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : (obj_ == kMulticlass || obj_ == kMulticlassOva) ? "multi_logloss"
                     : cfg_.objective);
   for (const std::string& m : names) {
     if (m == "None" || m == "none" || m == "null" || m == "na" || m == "custom") continue;
@@ -55,7 +55,8 @@ void Booster::InitMetrics() {
     else if (m == "l1" || m == "mae" || m == "mean_absolute_error" || m == "regression_l1") metrics_.push_back({kEvL1, "l1"});
     else if (m == "quantile") metrics_.push_back({kEvQuantile, "quantile"});
     else if (m == "mape" || m == "mean_absolute_percentage_error") metrics_.push_back({kEvMape, "mape"});
-    else if (m == "multi_logloss" || m == "multiclass" || m == "softmax") metrics_.push_back({kEvMultiLogloss, "multi_logloss"});
+    else if (m == "gamma_deviance" || m == "gamma-deviance") metrics_.push_back({kEvGammaDeviance, "gamma_deviance"});
+    else if (m == "multi_logloss" || m == "multiclass" || m == "softmax" || m == "multiclassova" || m == "multiclass_ova" || m == "ova" || m == "ovr") metrics_.push_back({kEvMultiLogloss, "multi_logloss"});
     else if (m == "multi_error") metrics_.push_back({kEvMultiError, "multi_error"});
     else if (m == "ndcg" || m == "lambdarank" || m == "rank_xendcg" || m == "xendcg") {
       std::vector<int> at = cfg_.eval_at;
@@ -166,15 +167,16 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
   bool ndcg_done = false;
   for (const MetricSpec& m : metrics_) {
     if (m.kind == kEvMultiLogloss || m.kind == kEvMultiError) {
-      LGB_CHECK(obj_ == kMulticlass, "metric=%s needs objective=multiclass", m.name.c_str());
-      k_metric_multi<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, K_, m.kind == kEvMultiLogloss ? 0 : 1, d_mpart_.p);
+      LGB_CHECK(obj_ == kMulticlass || obj_ == kMulticlassOva, "metric=%s needs objective=multiclass / multiclassova", m.name.c_str());
+      k_metric_multi<<<kMetricBlocks, kMetricThreads, 0, stream_>>>(score, ds->d_label.p, w, n, K_, m.kind == kEvMultiLogloss ? 0 : 1, d_mpart_.p,
+                                                                    obj_ == kMulticlassOva ? cfg_.sigmoid : 0.0);
       k_metric_final<<<1, kMetricThreads, 0, stream_>>>(d_mpart_.p, kMetricBlocks, d_mout_.p);
       LGB_CUDA(cudaMemcpyAsync(h, d_mout_.p, sizeof(double) * 2, cudaMemcpyDeviceToHost, stream_));
       LGB_CUDA(cudaStreamSynchronize(stream_));
       out->push_back(h[0] / h[1]);
       continue;
     }
-    LGB_CHECK(obj_ != kMulticlass, "metric=%s is not defined for objective=multiclass (multi_logloss, multi_error)", m.name.c_str());
+    LGB_CHECK(obj_ != kMulticlass && obj_ != kMulticlassOva, "metric=%s is not defined for multiclass objectives (multi_logloss, multi_error)", m.name.c_str());
     if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || m.kind >= kEvHuber) {
       const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError
                        : m.kind >= kEvL1 ? kMetricL1 + (m.kind - kEvL1) : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;
@@ -185,7 +187,7 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
       LGB_CUDA(cudaMemcpyAsync(h, d_mout_.p, sizeof(double) * 2, cudaMemcpyDeviceToHost, stream_));
       LGB_CUDA(cudaStreamSynchronize(stream_));
       const double v = h[0] / h[1];
-      out->push_back(m.kind == kEvRmse ? std::sqrt(v) : v);
+      out->push_back(m.kind == kEvRmse ? std::sqrt(v) : m.kind == kEvGammaDeviance ? h[0] * 2 : v);      // GammaDevianceMetric::AverageLoss: sum_loss * 2
     } else if (m.kind == kEvAuc) {
       const int ni = static_cast<int>(n);
       d_auc_keys_[0].Reserve(n); d_auc_keys_[1].Reserve(n); d_auc_idx_[0].Reserve(n); d_auc_idx_[1].Reserve(n);

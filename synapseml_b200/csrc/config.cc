@@ -138,6 +138,7 @@ void Config::Set(const std::string& params) {
   if (has("label_gain")) label_gain = ToList<double>("label_gain", kv["label_gain"]);
   if (has("eval_at")) eval_at = ToList<int>("eval_at", kv["eval_at"]);
   if (has("categorical_feature")) categorical_feature = ToList<int>("categorical_feature", kv["categorical_feature"]);
+  if (has("max_bin_by_feature")) max_bin_by_feature = ToList<int>("max_bin_by_feature", kv["max_bin_by_feature"]);
   GET_I(max_cat_to_onehot); GET_I(max_cat_threshold); GET_I(min_data_per_group); GET_D(cat_smooth); GET_D(cat_l2);
 #undef GET_I
 #undef GET_D

@@ -68,6 +68,7 @@ struct Config {
   // categorical features: column indexes (LightGBMBase.scala:162-198 resolves slot names to indexes before the native call) and the
   // knobs of the categorical split search (upstream config.h defaults; CategoricalParams in params/TrainParams.scala)
   std::vector<int> categorical_feature;
+  std::vector<int> max_bin_by_feature;      // one max_bin per column (dataset construction only, as upstream)
   int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
   double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // canonical key -> value as received (echoed into the model's parameters block)

@@ -379,9 +379,10 @@ __device__ int K1CategoricalBlock(const double* dv, int* dc, int* ci, int nd, in
 __global__ void __launch_bounds__(kK1Threads) k1_find_bin(const double* sorted, const long long* seg_off, const int* na_cnt_arr, int nfeat,
                                                         K1Params p, double* distinct, int* counts, int* starts, double* bounds, double* tmp,
                                                         double* upper, double* lower, int* cib, K1Meta* meta,
-                                                        const unsigned char* __restrict__ is_cat) {
+                                                        const unsigned char* __restrict__ is_cat, const int* __restrict__ max_bin_by_feature) {
   const int f = blockIdx.x;
   if (f >= nfeat) return;
+  if (max_bin_by_feature != nullptr) p.max_bin = max_bin_by_feature[f];      // p is this CTA's own copy
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ int s_warp[kK1Threads / 32];
   __shared__ int s_carry, s_nd;
@@ -871,7 +872,19 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   p.use_missing = c.use_missing;
   p.zero_as_missing = c.zero_as_missing;
   p.total_sample_cnt = num_sample_row;
-  p.bstride = any_cat ? std::max(c.max_bin + 4, kMaxBinsPerFeature + 4) : c.max_bin + 4;      // a categorical feature may exceed max_bin bins
+  int widest = c.max_bin;
+  DevBuf<int> d_mbf;
+  if (!c.max_bin_by_feature.empty()) {      // DatasetLoader::ConstructFromSampleData: one max_bin per column
+    LGB_CHECK(static_cast<int>(c.max_bin_by_feature.size()) == ncol, "max_bin_by_feature has %d values for %d columns",
+              static_cast<int>(c.max_bin_by_feature.size()), ncol);
+    for (int v : c.max_bin_by_feature) {
+      LGB_CHECK(v >= 2 && v <= kMaxWideBins, "max_bin_by_feature value %d is outside [2, %d]", v, kMaxWideBins);
+      widest = std::max(widest, v);
+    }
+    d_mbf.Alloc(ncol);
+    LGB_CUDA(cudaMemcpy(d_mbf.p, c.max_bin_by_feature.data(), sizeof(int) * ncol, cudaMemcpyHostToDevice));
+  }
+  p.bstride = any_cat ? std::max(widest + 4, kMaxBinsPerFeature + 4) : widest + 4;      // a categorical feature may exceed max_bin bins
   DevBuf<unsigned char> d_is_cat;
   if (any_cat) {
     d_is_cat.Alloc(ncol);
@@ -884,7 +897,8 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   d_bnd.Alloc(bs); d_tmp.Alloc(bs); d_up.Alloc(bs); d_lo.Alloc(bs); d_cib.Alloc(bs);
   d_meta.Alloc(ncol);
   k1_find_bin<<<ncol, kK1Threads>>>(d_sorted.p, d_off.p, d_na.p, ncol, p, d_distinct.p, d_counts.p, d_starts.p, d_bnd.p, d_tmp.p,
-                                    d_up.p, d_lo.p, d_cib.p, d_meta.p, any_cat ? d_is_cat.p : nullptr);
+                                    d_up.p, d_lo.p, d_cib.p, d_meta.p, any_cat ? d_is_cat.p : nullptr,
+                                    c.max_bin_by_feature.empty() ? nullptr : d_mbf.p);
   LGB_CUDA(cudaGetLastError());
   LGB_CUDA(cudaDeviceSynchronize());
   std::vector<K1Meta> hmeta(ncol);

@@ -58,10 +58,14 @@ __device__ __forceinline__ void GradL2Row(double score, float label, bool has_w,
   }
 }
 
+// pos_class < 0: positive = label > 0 (binary); otherwise positive = "label == pos_class" (one class of multiclassova)
 __global__ void k_grad_binary(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
-                              float* __restrict__ grad, float* __restrict__ hess, int n, double sigmoid, double lw_neg, double lw_pos) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    GradBinaryRow(score[i], label[i], weight != nullptr, weight ? weight[i] : 0.0f, sigmoid, lw_neg, lw_pos, grad + i, hess + i);
+                              float* __restrict__ grad, float* __restrict__ hess, int n, double sigmoid, double lw_neg, double lw_pos,
+                              int pos_class = -1) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float lab = pos_class < 0 ? label[i] : (static_cast<int>(label[i]) == pos_class ? 1.0f : 0.0f);
+    GradBinaryRow(score[i], lab, weight != nullptr, weight ? weight[i] : 0.0f, sigmoid, lw_neg, lw_pos, grad + i, hess + i);
+  }
 }
 
 __global__ void k_grad_l2(const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
@@ -360,8 +364,10 @@ __global__ void k_quantize(const float* __restrict__ grad, const float* __restri
 // Bagging (upstream src/boosting/bagging.hpp, BaggingHelper): every row draws once from the LCG stream of its 1024-row block
 // (seeded bagging_seed + block; the streams run on from one re-bagging to the next) and is in the bag when the 15-bit draw / 32768
 // is below bagging_fraction.  One thread per block; writes the bag as a bit per row and adds the bag size to *count.
+// label != nullptr: balanced bagging (BalancedBaggingHelper) — positives (label > 0) are kept with pos_fraction, the others with
+// `fraction` (= neg_bagging_fraction).
 __global__ void k_bag_sample(unsigned int* __restrict__ rand_state, int n, double fraction, unsigned int* __restrict__ bits,
-                             int* __restrict__ count) {
+                             int* __restrict__ count, const float* __restrict__ label = nullptr, double pos_fraction = 1.0) {
   const int blk = blockIdx.x * blockDim.x + threadIdx.x;
   if (blk >= (n + 1023) / 1024) return;
   unsigned int x = rand_state[blk];
@@ -372,7 +378,8 @@ __global__ void k_bag_sample(unsigned int* __restrict__ rand_state, int n, doubl
       if (blk * 1024 + w * 32 + j < n) {
         x = 214013u * x + 2531011u;
         const float u = static_cast<float>((x >> 16) & 0x7FFF) / 32768.0f;
-        if (static_cast<double>(u) < fraction) { word |= 1u << j; ++cnt; }
+        const double fr = (label != nullptr && label[blk * 1024 + w * 32 + j] > 0.0f) ? pos_fraction : fraction;
+        if (static_cast<double>(u) < fr) { word |= 1u << j; ++cnt; }
       }
     }
     bits[blk * 32 + w] = word;

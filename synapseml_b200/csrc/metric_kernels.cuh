@@ -17,7 +17,7 @@ constexpr int kMetricBlocks = 592;
 constexpr int kMetricThreads = 256;
 
 enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2, kMetricHuber = 3, kMetricFair = 4, kMetricPoisson = 5,
-                   kMetricGamma = 6, kMetricTweedie = 7, kMetricL1 = 8, kMetricQuantile = 9, kMetricMape = 10 };
+                   kMetricGamma = 6, kMetricTweedie = 7, kMetricL1 = 8, kMetricQuantile = 9, kMetricMape = 10, kMetricGammaDeviance = 11 };
 
 __device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -69,6 +69,9 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
         loss = delta < 0 ? (p0 - 1.0f) * delta : p0 * delta;
       } else if (kind == kMetricMape) {
         loss = fabs(lab - t) / fmax(1.0, fabs(lab));
+      } else if (kind == kMetricGammaDeviance) {  // GammaDevianceMetric::LossOnPoint
+        const double tmp = lab / (t + 1.0e-9);
+        loss = tmp - (tmp > 0.0 ? log(tmp) : -INFINITY) - 1;
       } else {                                    // tweedie, p0 = rho
         const double sc = t < 1e-10 ? 1e-10 : t;
         const double a = lab * exp((1 - p0) * log(sc)) / (1 - p0);
@@ -96,7 +99,7 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
 // (multi_error_top_k = 1).
 __global__ void __launch_bounds__(kMetricThreads) k_metric_multi(const double* __restrict__ score, const float* __restrict__ label,
                                                                   const float* __restrict__ weight, long long n, int K, int kind,
-                                                                  double2* __restrict__ partial) {
+                                                                  double2* __restrict__ partial, double ova_sigmoid = 0.0) {
   __shared__ double s_w[8];
   const double kEps = (double)1e-15f;
   double sl = 0.0, sw = 0.0;
@@ -116,7 +119,8 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_multi(const double* _
       num_larger += sc >= ref;
     }
     double loss;
-    if (kind == 0) { const double p = pl / wsum; loss = p > kEps ? -log(p) : -log(kEps); }
+    // the loss sees the objective's ConvertOutput: softmax, or (multiclassova, ova_sigmoid > 0) one sigmoid per class
+    if (kind == 0) { const double p = ova_sigmoid > 0.0 ? 1.0 / (1.0 + exp(-ova_sigmoid * ref)) : pl / wsum; loss = p > kEps ? -log(p) : -log(kEps); }
     else loss = num_larger > 1 ? 1.0 : 0.0;
     sl += loss * w; sw += w;
   }

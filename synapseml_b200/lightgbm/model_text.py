@@ -112,6 +112,12 @@ class TextModel:
 
     def predict(self, X):
         raw = self.predict_raw(X)
+        if self.objective.startswith("multiclassova"):      # MulticlassOVA::ConvertOutput: one sigmoid per class
+            sig = 1.0
+            for tok in self.objective.split():
+                if tok.startswith("sigmoid:"):
+                    sig = float(tok.split(":")[1])
+            return 1.0 / (1.0 + np.exp(-sig * raw))
         if self.objective.startswith("multiclass"):
             e = np.exp(raw - raw.max(axis=1, keepdims=True))
             return e / e.sum(axis=1, keepdims=True)

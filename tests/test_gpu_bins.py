@@ -136,3 +136,23 @@ def test_serialized_reference_round_trip_and_errors(native):
         validate(native.LGBM_DatasetPushRowsWithMetadata(nd2.handle, bad.ctypes.data_as(C.c_void_p), 1, 4, bad.shape[1], 0, None, None, None, None, 0))
     nd.free()
     nd2.free()
+
+
+def test_max_bin_by_feature(native, oracle):
+    """max_bin_by_feature (GeneralParams.maxBinByFeature, params/TrainParams.scala) at dataset construction: one max_bin per column, some
+    above 255 (several uint8 columns, csrc/dataset.h), some tiny."""
+    X, y = S.higgs_shape(30000, f=8)
+    params = "max_bin=255 min_data_in_leaf=20 max_bin_by_feature=4,300,17,3,255,1000,64,2"
+    nd = NativeDataset(X, y, params, micro_batches=[4096, 100])
+    oref, (ods,), _ = oracle_dataset(oracle, X, y, params)
+    assert_same_mappers(nd, oref, 8)
+    assert_same_bins_logical(nd, ods)
+    bins = [nd.feature_info(j)["num_bin"] for j in range(8)]
+    assert bins[0] <= 4 and bins[1] > 255 and bins[5] > 255 and bins[2] <= 17
+    nd.free()
+
+
+def assert_same_bins_logical(nd, ods):
+    assert nd.num_used() == ods.num_used_feature()
+    for j in range(nd.num_used()):
+        assert np.array_equal(nd.bin_column(j).astype(np.uint16), ods.bin_column(j)), j

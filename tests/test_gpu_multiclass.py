@@ -100,3 +100,53 @@ def test_estimator_infers_num_class_and_scores_with_softmax(native):
     # leaf indices: one per tree
     leaves = model.predict_leaf(X[:100])
     assert leaves.size == 100 * len(m.trees)
+
+
+@pytest.mark.parametrize("variant", ["plain", "weighted_unbalanced"])
+def test_multiclassova_matches_the_oracle(native, oracle, variant):
+    """objective=multiclassova (named by the reference's objective doc, LightGBMParams.scala:383-386): one binary log-loss problem per
+    class (upstream MulticlassOVA), K trees per iteration."""
+    X, y = three_class(60000)
+    w = np.random.Generator(np.random.PCG64(4)).uniform(0.5, 2.0, len(y)).astype(np.float32) if variant != "plain" else None
+    extra = " is_unbalance=true sigmoid=1.5" if variant != "plain" else ""
+    params = ("objective=multiclassova num_class=3 num_leaves=31 learning_rate=0.2 max_bin=63 min_data_in_leaf=20 use_quantized_grad=true "
+              "stochastic_rounding=false verbosity=-1" + extra)
+    nd, nb, ob = train_both(oracle, X, y, params, 1, weight=w)
+    g, h = nb.gradients()
+    og, oh = ob.gradients()
+    assert np.array_equal(g, og) and np.array_equal(h, oh)          # the first iteration's gradients of all three classes
+    for _ in range(7):
+        assert nb.update() == ob.update_one_iter()
+    ms = nb.model()
+    assert strip_parameters(ms) == strip_parameters(ob.save_model_to_string())
+    assert "objective=multiclassova num_class:3 sigmoid:%s" % ("1.5" if extra else "1") in ms and "num_tree_per_iteration=3" in ms
+    assert np.array_equal(nb.scores(), ob.scores())
+    nb.free()
+    nd.free()
+
+
+def test_multiclassova_estimator_scores_with_one_sigmoid_per_class(native):
+    from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LocalDataFrame
+    X, y = three_class(40000)
+    est = LightGBMClassifier(objective="multiclassova", numIterations=10, numLeaves=15, samplingMode="fixed", microBatchSize=4096,
+                             isProvideTrainingMetric=True, metric="multi_logloss,multi_error")
+    model = est.fit(LocalDataFrame.from_arrays(X, y, num_partitions=3))
+    m = TextModel(model.model_str)
+    out = model.transform(X[:8000])
+    assert out["rawPrediction"].shape == (8000, 3)
+    assert np.array_equal(out["rawPrediction"], m.predict_raw(X[:8000]))
+    assert np.allclose(out["probability"], 1.0 / (1.0 + np.exp(-m.predict_raw(X[:8000]))), rtol=1e-12, atol=1e-15)
+    assert (out["prediction"] == y[:8000]).mean() > 0.85
+    last = est.performance_measures["evalHistory"][-1][0]
+    p = m.predict(X)
+    yi = y.astype(int)
+    logloss = -np.log(np.maximum(p[np.arange(len(y)), yi], 1e-15)).mean()
+    raw = m.predict_raw(X)
+    err = ((raw >= raw[np.arange(len(y)), yi][:, None]).sum(axis=1) > 1).mean()
+    assert abs(last["multi_logloss"] - logloss) < 1e-10 and abs(last["multi_error"] - err) < 1e-12
+    # the model string reloads as a multiclassova model
+    from synapseml_b200.lightgbm.booster import LightGBMBooster
+    lb = LightGBMBooster(model_str=model.model_str)
+    assert lb.num_classes() == 3
+    assert np.allclose(lb.predict_for_mat(X[:100], LightGBMBooster.PREDICT_NORMAL).reshape(100, 3), out["probability"][:100], rtol=1e-12)
+    lb.free_native_memory()

@@ -86,6 +86,23 @@ def test_default_metric_follows_the_objective(native):
     nd.free()
 
 
+def test_gamma_deviance_metric(native):
+    """metric=gamma_deviance (named by the reference's metric doc, LightGBMParams.scala:593): 2 * sum(w * (y / p - log(y / p) - 1))."""
+    X, y = count_data(20000, positive=True)
+    params = "objective=gamma metric=gamma,gamma_deviance num_leaves=15 max_bin=63 verbosity=-1"
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    for _ in range(5):
+        nb.update()
+    n = C.c_int()
+    out = np.zeros(4)
+    validate(lightgbmlib().LGBM_BoosterGetEval(nb.handle, 0, C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+    t = y / (np.exp(nb.scores()) + 1e-9)
+    assert n.value == 2 and np.isclose(out[1], 2 * np.sum(t - np.log(t) - 1), rtol=1e-10)
+    nb.free()
+    nd.free()
+
+
 def test_regressor_estimator_with_tweedie(native):
     X, y = count_data(30000, positive=False)
     df = LocalDataFrame.from_arrays(X, y, num_partitions=2)

@@ -39,6 +39,8 @@ QUANT_CASES = {
     "stochastic": "objective=binary num_leaves=31 max_bin=255 stochastic_rounding=true seed=5",
     "l2": "objective=regression num_leaves=31 max_bin=63 min_data_in_leaf=20",
     "min_hessian": "objective=binary num_leaves=31 max_bin=63 min_sum_hessian_in_leaf=50 min_data_in_leaf=100",
+    # posBaggingFraction / negBaggingFraction (LightGBMParams.scala; upstream BalancedBaggingHelper)
+    "balanced_bagging": "objective=binary num_leaves=15 max_bin=63 bagging_freq=1 pos_bagging_fraction=0.4 neg_bagging_fraction=0.8 bagging_seed=7",
 }
 
 
