@@ -297,7 +297,9 @@ class LightGBMBase:
             payload = [model_str]
             dist.broadcast_object_list(payload, src=0)
             model_str = payload[0]
-        return self._make_model(model_str)
+        model = self._make_model(model_str)
+        model.best_iteration = self.best_iteration
+        return model
 
     def add_custom_train_params(self, train_params, df, dist):
         """LightGBMBase.addCustomTrainParams: estimator-specific additions that need the data (the classifier's numClass)."""
@@ -355,6 +357,45 @@ class LightGBMModelBase:
 
     def getFeatureImportances(self, importance_type="split"):
         return self._native().get_feature_importances(importance_type)
+
+    # ---- LightGBMModelMethods.scala:28-96
+    def getFeatureShaps(self, features):
+        """Local SHAP values of one instance (featuresShap): numClasses * (numFeatures + 1) values."""
+        return self._native().predict_for_mat(np.asarray(features, dtype=np.float64).reshape(1, -1), LightGBMBooster.PREDICT_CONTRIB)[0].tolist()
+
+    def getDenseFeatureShaps(self, features):
+        return self.getFeatureShaps(features)
+
+    def getSparseFeatureShaps(self, size, indices, values):
+        row = np.zeros(size, dtype=np.float64)
+        row[np.asarray(indices, dtype=np.int64)] = np.asarray(values, dtype=np.float64)
+        return self.getFeatureShaps(row)
+
+    def getBoosterBestIteration(self):
+        """-1 unless early stopping was triggered (LightGBMBooster.scala:247)."""
+        return -1 if getattr(self, "best_iteration", None) is None else int(self.best_iteration)
+
+    def getBoosterNumTotalModel(self):
+        return self._native().num_total_model()
+
+    def getBoosterNumTotalIterations(self):
+        return self._native().num_total_model() // max(1, self._model.num_tree_per_iteration)      # LightGBMBooster.scala:518
+
+    def getBoosterNumFeatures(self):
+        return self._native().num_features()
+
+    def getBoosterNumClasses(self):
+        return self._native().num_classes()
+
+    @classmethod
+    def loadNativeModelFromString(cls, model):
+        """LightGBMClassificationModel / RegressionModel / RankerModel .loadNativeModelFromString."""
+        return cls(model)
+
+    @classmethod
+    def loadNativeModelFromFile(cls, filename):
+        with open(filename) as f:
+            return cls(f.read())
 
 
 class LightGBMClassificationModel(LightGBMModelBase):

@@ -140,3 +140,24 @@ def test_sparse_partitions_give_the_dense_model(native):
     bulk_sparse = LightGBMClassifier(dataTransferMode="bulk", **kw).fit(LocalDataFrame(parts)).getNativeModel()
     assert bulk_sparse.split("parameters:")[0] == dense.split("parameters:")[0]
 
+
+
+def test_model_methods(native, tmp_path):
+    """LightGBMModelMethods.scala:19-107 and the models' companion objects (loadNativeModelFromFile / ...FromString)."""
+    from synapseml_b200.lightgbm.estimators import LightGBMClassificationModel
+    X, y = S.higgs_shape(20000)
+    model = LightGBMClassifier(numIterations=7, numLeaves=15, samplingMode="fixed").fit(LocalDataFrame.from_arrays(X, y))
+    assert model.getBoosterNumTotalIterations() == 7 and model.getBoosterNumTotalModel() == 7
+    assert model.getBoosterNumFeatures() == X.shape[1] and model.getBoosterNumClasses() == 1
+    assert model.getBoosterBestIteration() == -1                          # no early stopping
+    shap = np.array(model.getFeatureShaps(X[3]))
+    assert shap.shape == (X.shape[1] + 1,) and np.isclose(shap.sum(), model.predict_raw(X[3:4])[0], atol=1e-9)
+    nz = np.flatnonzero(X[3])
+    assert np.allclose(model.getSparseFeatureShaps(X.shape[1], nz, X[3][nz]), shap) and np.allclose(model.getDenseFeatureShaps(X[3]), shap)
+    imp = model.getFeatureImportances("split")
+    assert len(imp) == X.shape[1] and sum(imp) == sum(t.num_leaves - 1 for t in model._model.trees)
+    path = tmp_path / "model.txt"
+    model.saveNativeModel(str(path))
+    for again in (LightGBMClassificationModel.loadNativeModelFromFile(str(path)), LightGBMClassificationModel.loadNativeModelFromString(model.getNativeModel())):
+        assert again.getNativeModel() == model.getNativeModel()
+        assert np.array_equal(again.transform(X[:500])["probability"], model.transform(X[:500])["probability"])
