@@ -198,6 +198,9 @@ struct Config {
   // categorical features (upstream config.h defaults): column indexes, and the knobs of the categorical split search
   std::vector<int> categorical_feature;
   std::vector<int> max_bin_by_feature;
+  std::vector<int> monotone_constraints;      // per column: +1 / -1 / 0
+  std::string monotone_constraints_method = "basic";
+  double monotone_penalty = 0.0;
   int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
   double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // everything seen, canonical key -> value (first writer wins)
@@ -232,6 +235,9 @@ struct Config {
         {"num_machine", "num_machines"},
         {"verbose", "verbosity"},
         {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"},
+        {"mc", "monotone_constraints"}, {"monotone_constraint", "monotone_constraints"}, {"monotonic_cst", "monotone_constraints"},
+        {"monotone_constraining_method", "monotone_constraints_method"}, {"mc_method", "monotone_constraints_method"},
+        {"monotone_splits_penalty", "monotone_penalty"}, {"ms_penalty", "monotone_penalty"}, {"mc_penalty", "monotone_penalty"},
         {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"}, {"cat_column", "categorical_feature"},
         {"categorical_features", "categorical_feature"},
     };
@@ -337,6 +343,9 @@ struct Config {
     if (has("eval_at")) eval_at = ParseList<int>(kv["eval_at"]);
     if (has("categorical_feature")) categorical_feature = ParseList<int>(kv["categorical_feature"]);
     if (has("max_bin_by_feature")) max_bin_by_feature = ParseList<int>(kv["max_bin_by_feature"]);
+    if (has("monotone_constraints")) monotone_constraints = ParseList<int>(kv["monotone_constraints"]);
+    if (has("monotone_constraints_method")) monotone_constraints_method = kv["monotone_constraints_method"];
+    getd("monotone_penalty", &monotone_penalty);
     geti("max_cat_to_onehot", &max_cat_to_onehot); geti("max_cat_threshold", &max_cat_threshold); geti("min_data_per_group", &min_data_per_group);
     getd("cat_smooth", &cat_smooth); getd("cat_l2", &cat_l2);
     // objective aliases

@@ -31,6 +31,7 @@ struct SplitInfo {
   double left_sum_gradient = 0.0, left_sum_hessian = 0.0, right_sum_gradient = 0.0, right_sum_hessian = 0.0;
   int64_t left_int_g = 0, left_int_h = 0, right_int_g = 0, right_int_h = 0;
   bool default_left = true;
+  int monotone_type = 0;
   std::vector<uint32_t> cat_threshold;      // categorical split: the bins that go left (num_cat_threshold = its size), else empty
   bool categorical = false;
   void Reset() { *this = SplitInfo(); }
@@ -49,6 +50,11 @@ struct SplitParams {
   // categorical split search
   int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
   double cat_smooth = 10.0, cat_l2 = 10.0;
+  // monotone constraints, method "basic" (USE_MC is on for every feature once any column is constrained): the leaf's output range
+  // and the searched feature's direction
+  bool mc = false;
+  double cmin = -std::numeric_limits<double>::infinity(), cmax = std::numeric_limits<double>::infinity();
+  int mono = 0;
 };
 
 inline double ThresholdL1(double s, double l1) {
@@ -71,8 +77,19 @@ inline double LeafGain(double g, double h, const SplitParams& p) {
   }
   return LeafGainGivenOutput(g, h, p, LeafOutput(g, h, p));
 }
+// CalculateSplittedLeafOutput<USE_MC>: the output clamped to the leaf's range
+inline double LeafOutputC(double g, double h, const SplitParams& p) {
+  double ret = LeafOutput(g, h, p);
+  if (p.mc) { if (ret < p.cmin) ret = p.cmin; else if (ret > p.cmax) ret = p.cmax; }
+  return ret;
+}
+// GetSplitGains<USE_MC>: with constraints the gain is taken at the clamped outputs, and a split that breaks the feature's direction
+// has none
 inline double SplitGain(double lg, double lh, double rg, double rh, const SplitParams& p) {
-  return LeafGain(lg, lh, p) + LeafGain(rg, rh, p);
+  if (!p.mc) return LeafGain(lg, lh, p) + LeafGain(rg, rh, p);
+  const double lo = LeafOutputC(lg, lh, p), ro = LeafOutputC(rg, rh, p);
+  if ((p.mono > 0 && lo > ro) || (p.mono < 0 && lo < ro)) return 0;
+  return LeafGainGivenOutput(lg, lh, p, lo) + LeafGainGivenOutput(rg, rh, p, ro);
 }
 
 // Float-histogram threshold search for one numerical feature (FindBestThresholdSequentially, both directions).
@@ -113,6 +130,7 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
         if (gain <= min_gain_shift) continue;
         splittable = true;
         if (gain > best_gain) {
+          if (p.mc && p.cmin > p.cmax) continue;
           best_left_count = lc; best_lg = lg; best_lh = lh;
           best_threshold = static_cast<uint32_t>(b - 1);
           best_gain = gain;
@@ -135,6 +153,7 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
         if (gain <= min_gain_shift) continue;
         splittable = true;
         if (gain > best_gain) {
+          if (p.mc && p.cmin > p.cmax) continue;
           best_left_count = lc; best_lg = lg; best_lh = lh;
           best_threshold = static_cast<uint32_t>(b);
           best_gain = gain;
@@ -143,11 +162,11 @@ inline bool FindBestThresholdFloat(const double* hist, const BinMapper& m, doubl
     }
     if (splittable && best_gain > out->gain + min_gain_shift) {
       out->threshold = best_threshold;
-      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_output = LeafOutputC(best_lg, best_lh, p);
       out->left_count = best_left_count;
       out->left_sum_gradient = best_lg;
       out->left_sum_hessian = best_lh - kEpsilon;
-      out->right_output = LeafOutput(sum_gradient - best_lg, sum_hessian - best_lh, p);
+      out->right_output = LeafOutputC(sum_gradient - best_lg, sum_hessian - best_lh, p);
       out->right_count = num_data - best_left_count;
       out->right_sum_gradient = sum_gradient - best_lg;
       out->right_sum_hessian = sum_hessian - best_lh - kEpsilon;
@@ -204,7 +223,7 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
         double gain = SplitGain(slg, slh, srg, srh, p);
         if (gain <= min_gain_shift) continue;
         splittable = true;
-        if (gain > best_gain) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b - 1); best_gain = gain; }
+        if (gain > best_gain && !(p.mc && p.cmin > p.cmax)) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b - 1); best_gain = gain; }
       }
     } else {
       int64_t lg = 0, lh = 0;
@@ -223,7 +242,7 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
         double gain = SplitGain(slg, slh, srg, srh, p);
         if (gain <= min_gain_shift) continue;
         splittable = true;
-        if (gain > best_gain) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b); best_gain = gain; }
+        if (gain > best_gain && !(p.mc && p.cmin > p.cmax)) { best_lg = lg; best_lh = lh; best_threshold = static_cast<uint32_t>(b); best_gain = gain; }
       }
     }
     if (splittable && best_gain > out->gain + min_gain_shift) {
@@ -231,11 +250,11 @@ inline bool FindBestThresholdInt(const int64_t* hist, const BinMapper& m, int64_
       double blg = static_cast<double>(best_lg) * grad_scale, blh = static_cast<double>(best_lh) * hess_scale;
       double brg = static_cast<double>(rg) * grad_scale, brh = static_cast<double>(rh) * hess_scale;
       out->threshold = best_threshold;
-      out->left_output = LeafOutput(blg, blh, p);
+      out->left_output = LeafOutputC(blg, blh, p);
       out->left_count = RoundInt(static_cast<double>(best_lh) * cnt_factor);
       out->left_sum_gradient = blg; out->left_sum_hessian = blh;
       out->left_int_g = best_lg; out->left_int_h = best_lh;
-      out->right_output = LeafOutput(brg, brh, p);
+      out->right_output = LeafOutputC(brg, brh, p);
       out->right_count = RoundInt(static_cast<double>(rh) * cnt_factor);
       out->right_sum_gradient = brg; out->right_sum_hessian = brh;
       out->right_int_g = rg; out->right_int_h = rh;
@@ -369,16 +388,16 @@ inline bool FindBestThresholdCategorical(const HistT* hist, const BinMapper& m, 
     if (QUANT) {
       const int64_t rg = int_sum_g - best_int_lg, rh = int_sum_h - best_int_lh;
       const double brg = static_cast<double>(rg) * grad_scale, brh = static_cast<double>(rh) * hess_scale;
-      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_output = LeafOutputC(best_lg, best_lh, p);
       out->left_sum_gradient = best_lg; out->left_sum_hessian = best_lh;
       out->left_int_g = best_int_lg; out->left_int_h = best_int_lh;
-      out->right_output = LeafOutput(brg, brh, p);
+      out->right_output = LeafOutputC(brg, brh, p);
       out->right_sum_gradient = brg; out->right_sum_hessian = brh;
       out->right_int_g = rg; out->right_int_h = rh;
     } else {
-      out->left_output = LeafOutput(best_lg, best_lh, p);
+      out->left_output = LeafOutputC(best_lg, best_lh, p);
       out->left_sum_gradient = best_lg; out->left_sum_hessian = best_lh - kEpsilon;
-      out->right_output = LeafOutput(sum_gradient - best_lg, sum_hessian - best_lh, p);
+      out->right_output = LeafOutputC(sum_gradient - best_lg, sum_hessian - best_lh, p);
       out->right_sum_gradient = sum_gradient - best_lg; out->right_sum_hessian = sum_hessian - best_lh - kEpsilon;
     }
     out->gain = best_gain - min_gain_shift;
@@ -453,6 +472,7 @@ class Booster {
   int iter = 0;
   // objective state
   enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA } obj = OBJ_L2;
+  std::vector<int> mono_inner;             // monotone direction per inner feature (empty: no constraints at all)
   bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA; }
   std::vector<double> ova_label_weights, ova_suml;      // multiclassova: per class [neg, pos] label weights and the weighted positives
   double ova_sumw = 0.0;
@@ -483,6 +503,8 @@ class Booster {
   struct Leaf {
     double sum_g = 0, sum_h = 0; int64_t int_g = 0, int_h = 0;
     data_size_t count = 0;               // count used by the split finder (serial: true; dp: global estimate)
+    int depth = 0;
+    double cmin = -std::numeric_limits<double>::infinity(), cmax = std::numeric_limits<double>::infinity();      // BasicLeafConstraints entry
     SplitInfo best;
     std::vector<char> splittable;
   };
@@ -519,6 +541,11 @@ class Booster {
     }
     total_rows = off;
     has_weights = ds[0]->has_weight;
+    if (std::any_of(cfg.monotone_constraints.begin(), cfg.monotone_constraints.end(), [](int v) { return v != 0; })) {
+      if (cfg.monotone_constraints_method != "basic") throw std::runtime_error("oracle: only monotone_constraints_method=basic is restated");
+      if (static_cast<int>(cfg.monotone_constraints.size()) != ds[0]->num_total_features) throw std::runtime_error("oracle: monotone_constraints needs one value per column");
+      for (int f = 0; f < F; ++f) mono_inner.push_back(cfg.monotone_constraints[ds[0]->used_features[f]]);
+    }
     sp = {cfg.lambda_l1, cfg.lambda_l2, cfg.max_delta_step, cfg.min_gain_to_split, cfg.min_sum_hessian_in_leaf, cfg.min_data_in_leaf,
           cfg.max_cat_to_onehot, cfg.max_cat_threshold, cfg.min_data_per_group, cfg.cat_smooth, cfg.cat_l2};
     if (cfg.boosting == "gbdt") boost = BOOST_GBDT;
@@ -1246,18 +1273,26 @@ class Booster {
       const BinMapper& m = shards[0].ds->inner_mapper(f);
       SplitInfo si;
       bool ok;
+      SplitParams q = sp;
+      if (!mono_inner.empty()) { q.mc = true; q.cmin = L.cmin; q.cmax = L.cmax; q.mono = m.categorical ? 0 : mono_inner[f]; }
       if (m.categorical) {
         if (cfg.use_quantized_grad)
           ok = FindBestThresholdCategorical<true>(hist_i[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, L.int_g, L.int_h,
-                                                  grad_scale, hess_scale, L.count, sp, &si);
+                                                  grad_scale, hess_scale, L.count, q, &si);
         else
           ok = FindBestThresholdCategorical<false>(hist_f[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, 0, 0, 1.0, 1.0,
-                                                   L.count, sp, &si);
+                                                   L.count, q, &si);
       } else if (cfg.use_quantized_grad) {
         ok = FindBestThresholdInt(hist_i[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.int_g, L.int_h, grad_scale,
-                                  hess_scale, L.count, sp, &si);
+                                  hess_scale, L.count, q, &si);
       } else {
-        ok = FindBestThresholdFloat(hist_f[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, L.count, sp, &si);
+        ok = FindBestThresholdFloat(hist_f[leaf].data() + static_cast<size_t>(f) * B * 2, m, L.sum_g, L.sum_h, L.count, q, &si);
+      }
+      si.monotone_type = q.mono;
+      if (q.mono != 0) {      // LeafConstraintsBase::ComputeMonotoneSplitGainPenalty (SerialTreeLearner::ComputeBestSplitForFeature)
+        const double pen = cfg.monotone_penalty, depth = L.depth;
+        const double factor = pen >= depth + 1. ? kEpsilon : pen <= 1. ? 1. - pen / std::pow(2., depth) + kEpsilon : 1. - std::pow(2, pen - 1. - depth) + kEpsilon;
+        si.gain *= factor;
       }
       si.feature = f;
       si.real_feature = shards[0].ds->used_features[f];
@@ -1402,6 +1437,15 @@ class Booster {
     R.sum_g = bs.right_sum_gradient; R.sum_h = bs.right_sum_hessian; R.int_g = bs.right_int_g; R.int_h = bs.right_int_h;
     R.count = bs.right_count;
     L.splittable = parent_spl; R.splittable = parent_spl;
+    // BasicLeafConstraints::Update: the new leaf inherits the range; a numerical split on a constrained feature cuts both at the
+    // mean of the two outputs
+    R.cmin = L.cmin; R.cmax = L.cmax;
+    R.depth = L.depth = L.depth + 1;
+    if (!bs.categorical && bs.monotone_type != 0) {
+      const double mid = (bs.left_output + bs.right_output) / 2.0f;
+      if (bs.monotone_type < 0) { L.cmin = std::max(mid, L.cmin); R.cmax = std::min(mid, R.cmax); }
+      else { L.cmax = std::min(mid, L.cmax); R.cmin = std::max(mid, R.cmin); }
+    }
     L.best.Reset(); R.best.Reset();
   }
 

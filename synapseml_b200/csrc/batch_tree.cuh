@@ -59,6 +59,7 @@ struct NodeDev {
   int state;               // 0: leaf whose children are not known; 1: expanded (children known, split not committed); 2: committed
   int left, right;         // child nodes once expanded
   int pad_;
+  double cmin, cmax;       // monotone constraints: the output range of this leaf (BasicLeafConstraints entry)
   // what the replay needs to know about the children of an expanded node, written by the children's split search
   // ([0] = left child, [1] = right child), so that it never has to chase the child nodes
   int child_feat[2], child_count[2];
@@ -81,6 +82,10 @@ struct BatchItem {
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
   int is_cat, pad_;                             // categorical split: rows whose bin has its bit set in cat_bits go left
   unsigned int cat_bits[8];
+  // monotone constraints: the parent's output range, the split feature's direction and the two outputs (the children's ranges
+  // follow from them: BasicLeafConstraints::Update)
+  int mono, pad2_;
+  double cmin, cmax, left_output, right_output;
 };
 
 struct BatchCtrl {
@@ -203,6 +208,7 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
     NodeDev z;
     z.begin = 0; z.count = n_local; z.buf = -1; z.global_count = n_global; z.int_g = z.int_h = 0; z.sum_g = z.sum_h = 0.0;
     z.depth = 0; z.hist_slot = 0; z.state = 0; z.left = z.right = -1; z.pad_ = 0;
+    z.cmin = -INFINITY; z.cmax = INFINITY;
     z.child_feat[0] = z.child_feat[1] = -1; z.child_count[0] = z.child_count[1] = 0; z.child_gain[0] = z.child_gain[1] = KMINSCORE;
     z.best = EmptySplit(-1, -1);
     nodes[0] = z;
@@ -378,6 +384,11 @@ __device__ __forceinline__ void FindUnitWarp(const long long* work, int work_ele
     me.int_g = is_left ? it.left_int_g : it.right_int_g; me.int_h = is_left ? it.left_int_h : it.right_int_h;
     me.sum_g = is_left ? it.left_sum_g : it.right_sum_g; me.sum_h = is_left ? it.left_sum_h : it.right_sum_h;
     me.depth = it.child_depth;
+    me.cmin = it.cmin; me.cmax = it.cmax;
+    if (!it.is_cat && it.mono != 0) {      // BasicLeafConstraints::Update: both ranges are cut at the mean of the two outputs
+      const double mid = (it.left_output + it.right_output) / 2.0f;
+      if ((it.mono < 0) == is_left) me.cmin = fmax(mid, me.cmin); else me.cmax = fmin(mid, me.cmax);
+    }
     me.hist_slot = c == 0 ? it.fresh_slot : it.parent_slot;     // the larger child takes over the parent's slot
     me.state = 0; me.left = me.right = -1; me.pad_ = 0;
   }
@@ -468,6 +479,7 @@ __device__ __forceinline__ void FindUnitWarp(const long long* work, int work_ele
       N.begin = me.begin; N.count = me.count; N.buf = me.buf; N.global_count = me.global_count;
       N.int_g = me.int_g; N.int_h = me.int_h; N.sum_g = me.sum_g; N.sum_h = me.sum_h;
       N.depth = me.depth; N.hist_slot = me.hist_slot; N.state = me.state; N.left = me.left; N.right = me.right; N.pad_ = 0;
+      N.cmin = me.cmin; N.cmax = me.cmax;
       N.child_feat[0] = N.child_feat[1] = -1; N.child_count[0] = N.child_count[1] = 0;
       N.child_gain[0] = N.child_gain[1] = KMINSCORE;
     }
@@ -547,10 +559,12 @@ __global__ void __launch_bounds__(kFindWarps * 32, 2) k_bt_find_warp(const long 
   LGB_TRACE(ctrl, 32);
 }
 
+// EXT = false: the dataset has neither categorical nor wide features and no column is constrained — that code is compiled out, so
+// the plain numerical search is the kernel it was before those features existed (with them merely present the unit was 20 % slower).
 // ---- the same search with a 256-thread CTA per unit (one bin per thread, block-wide scans): one threshold per thread makes a
 // unit's latency half that of the warp form (4.4 vs 9.4 us, B200), so it is what narrow data uses, where a round has only a few
 // hundred units (C2: 28 x 2 x 8) and is bound by latency; the warp form wins when the units no longer fit one wave (C5: 32000).
-template <bool QUANT>
+template <bool QUANT, bool EXT>
 __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, long long* pool, const FeatureMetaDev* __restrict__ fmeta,
                                          NodeDev* nodes, BatchCtrl* ctrl, SplitDev* feat_best, unsigned char* splittable,
                                          const LearnerParams& P, int root, int f, int c, int k, int sub, const PeerTable* pt = nullptr) {
@@ -588,6 +602,11 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
     me.int_g = is_left ? it.left_int_g : it.right_int_g; me.int_h = is_left ? it.left_int_h : it.right_int_h;
     me.sum_g = is_left ? it.left_sum_g : it.right_sum_g; me.sum_h = is_left ? it.left_sum_h : it.right_sum_h;
     me.depth = it.child_depth;
+    me.cmin = it.cmin; me.cmax = it.cmax;
+    if (!it.is_cat && it.mono != 0) {      // BasicLeafConstraints::Update: both ranges are cut at the mean of the two outputs
+      const double mid = (it.left_output + it.right_output) / 2.0f;
+      if ((it.mono < 0) == is_left) me.cmin = fmax(mid, me.cmin); else me.cmax = fmin(mid, me.cmax);
+    }
     me.hist_slot = c == 0 ? it.fresh_slot : it.parent_slot;     // the larger child takes over the parent's slot
     me.state = 0; me.left = me.right = -1; me.pad_ = 0;
   }
@@ -608,7 +627,10 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   const size_t item_off = static_cast<size_t>(root ? 0 : k) * work_elems;
   // K5 for bin b of column `col`: this rank's (or all ranks') fresh sums, turned into the larger child's by subtracting them from
   // the parent's, and stored in the child's pool slot
-  auto child_bin = [&](int col, bool store) -> longlong2 {
+  // (explicit value captures: capturing the node record `me` by reference would pin that whole struct in local memory)
+  const int my_slot = me.hist_slot;
+  const bool subtract = !root && c == 1;
+  auto child_bin = [b, item_off, slot_stride, my_slot, subtract, parent_slot, work, pool, pt](int col, bool store) -> longlong2 {
     const size_t off = (static_cast<size_t>(col) * kBins + b) * 2;
     longlong2 v;
     if (pt != nullptr && pt->world > 0) {      // sum of all ranks' bins, read over peer memory
@@ -627,17 +649,19 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
     } else {
       v = *reinterpret_cast<const longlong2*>(work + item_off + off);
     }
-    if (!root && c == 1) {
+    if (subtract) {
       const longlong2 p = *reinterpret_cast<const longlong2*>(pool + static_cast<size_t>(parent_slot) * slot_stride + off);
       v.x = p.x - v.x; v.y = p.y - v.y;
     }
-    if (store) *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(me.hist_slot) * slot_stride + off) = v;
+    if (store) *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(my_slot) * slot_stride + off) = v;
     return v;
   };
   // a wide feature (more than 256 bins: several columns, dataset.h) is handled whole by the unit of its first column; the units
   // of its other columns have nothing to compute and report "no split"
-  longlong2 v = make_longlong2(0, 0);
-  if (fm.wide_cols == 0) v = child_bin(f, true);
+  // (the loads do not wait for the feature's description: one memory round trip, not two, on the unit's critical path)
+  const longlong2 v = child_bin(f, false);
+  if (!EXT || fm.wide_cols == 0)
+    *reinterpret_cast<longlong2*>(pool + static_cast<size_t>(my_slot) * slot_stride + (static_cast<size_t>(f) * kBins + b) * 2) = v;
   const bool used = root || splittable[static_cast<size_t>(parent) * F + f] != 0;
   SplitDev* fb = feat_best + static_cast<size_t>(root ? 0 : (k * 2 + c)) * F;
   unsigned char* spl = splittable + static_cast<size_t>(node) * F + f;
@@ -645,20 +669,25 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   // column sample of this tree (feature_fraction): a feature outside it has no split.  At the root it still runs the search,
   // because the leaf totals come out of it, and its result is discarded.
   const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
-  if (fm.wide_cols < 0) {
+  McCtx mc{0, 0, 0.0, 0.0};
+  if (EXT && P.monotone != nullptr) { mc.on = 1; mc.mono = fm.bin_type != 0 ? 0 : P.monotone[f]; mc.cmin = me.cmin; mc.cmax = me.cmax; }
+  if (EXT && fm.wide_cols < 0) {
     if (root) WideRootTotals(child_bin, fmeta[f + fm.wide_cols], f + fm.wide_cols, &tg, &th, sub);
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
-  } else if (fm.wide_cols > 0) {
+  } else if (EXT && fm.wide_cols > 0) {
     // the columns' sums are needed by the children whatever happens to this feature here (K5 runs for every column)
     BlockFindBestWide<QUANT>(child_bin, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
-                             fb + f, spl, &tg, &th, pool + static_cast<size_t>(me.hist_slot) * slot_stride, sub);
+                             fb + f, spl, &tg, &th, pool + static_cast<size_t>(me.hist_slot) * slot_stride, sub, mc, me.depth);
     if ((!used || !sampled) && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else if (!used || (!sampled && !root)) {
     if (b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }
   } else {
-    if (fm.bin_type != 0)
+    if (EXT && fm.bin_type != 0)
       BlockFindBestCat<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
-                              fb + f, spl, &tg, &th, sub);
+                              fb + f, spl, &tg, &th, sub, mc, me.depth);
+    else if (EXT && mc.on)
+      BlockFindBest<QUANT, true>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
+                                 fb + f, spl, &tg, &th, sub, mc, me.depth);
     else
       BlockFindBest<QUANT>(v.x, v.y, fm, f, root != 0, me.int_g, me.int_h, me.sum_g, me.sum_h, me.global_count, P, gscale, hscale,
                            fb + f, spl, &tg, &th, sub);
@@ -675,6 +704,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
       N.begin = me.begin; N.count = me.count; N.buf = me.buf; N.global_count = me.global_count;
       N.int_g = me.int_g; N.int_h = me.int_h; N.sum_g = me.sum_g; N.sum_h = me.sum_h;
       N.depth = me.depth; N.hist_slot = me.hist_slot; N.state = me.state; N.left = me.left; N.right = me.right; N.pad_ = 0;
+      N.cmin = me.cmin; N.cmax = me.cmax;
       N.child_feat[0] = N.child_feat[1] = -1; N.child_count[0] = N.child_count[1] = 0;
       N.child_gain[0] = N.child_gain[1] = KMINSCORE;
     }
@@ -737,7 +767,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   SubSync(sub);       // the sub-block's shared scratch is reused by its next unit
 }
 
-template <bool QUANT>
+template <bool QUANT, bool EXT>
 __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ work, int work_elems, long long* __restrict__ pool,
                                                  const FeatureMetaDev* __restrict__ fmeta, NodeDev* __restrict__ nodes,
                                                  BatchCtrl* __restrict__ ctrl, SplitDev* __restrict__ feat_best,
@@ -759,7 +789,7 @@ __global__ void __launch_bounds__(256) k_bt_find(const long long* __restrict__ w
     __syncthreads();
     if (!s_ok) return;
   }
-  FindUnit<QUANT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, 0, &pt);
+  FindUnit<QUANT, EXT>(work, work_elems, pool, fmeta, nodes, ctrl, feat_best, splittable, P, root, f, blockIdx.y, k, 0, &pt);
   LGB_TRACE(ctrl, 32);
 }
 
@@ -1212,6 +1242,8 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       it.feature = bs.feature; it.threshold = bs.threshold; it.default_left = bs.default_left;
       it.nan_bin = bs.nan_bin;
       it.is_cat = bs.is_cat; it.pad_ = 0;
+      it.mono = bs.monotone_type; it.pad2_ = 0; it.cmin = par.cmin; it.cmax = par.cmax;
+      it.left_output = bs.left_output; it.right_output = bs.right_output;
       #pragma unroll
       for (int w = 0; w < 8; ++w) it.cat_bits[w] = bs.cat_bits[w];
       it.src_begin = par.begin; it.src_count = par.count; it.src_buf = par.buf;

@@ -81,7 +81,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   // constructed dataset and goes on, which is what the reference's flow does — LightGBMBase.scala:374-386 never sends it there)
   if (cfg_.raw.count("max_bin_by_feature") && train->cfg.max_bin_by_feature.empty())
     LogWarning("Cannot change max_bin_by_feature after constructed Dataset handle.");
-  for (const char* key : {"monotone_constraints", "interaction_constraints", "forcedsplits_filename",
+  for (const char* key : {"interaction_constraints", "forcedsplits_filename",
                           "cegb_penalty_split", "linear_tree", "extra_trees", "path_smooth", "feature_contri"}) {
     auto it = cfg_.raw.find(key);
     if (it == cfg_.raw.end()) continue;
@@ -131,6 +131,27 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   find_warp_ = static_cast<long long>(F_) * 2 * kMaxBatch > 148LL * 8 * 2 && !net_->active();
   if (const char* env = getenv("LGB_B200_FIND_WARP")) find_warp_ = atoi(env) != 0;
   if (ds_->has_categorical || ds_->has_wide) find_warp_ = false;      // the categorical and the wide-feature search exist in the CTA form only
+  // monotone constraints (LightGBMParams.scala monotoneConstraints / monotoneConstraintsMethod / monotonePenalty), method "basic"
+  lp_.monotone = nullptr;
+  lp_.monotone_penalty = cfg_.monotone_penalty;
+  if (std::any_of(cfg_.monotone_constraints.begin(), cfg_.monotone_constraints.end(), [](int v) { return v != 0; })) {
+    LGB_CHECK(cfg_.monotone_constraints_method == "basic", "monotone_constraints_method=%s is not supported by this library (basic)",
+              cfg_.monotone_constraints_method.c_str());
+    LGB_CHECK(static_cast<int>(cfg_.monotone_constraints.size()) == ds_->num_total_features,
+              "monotone_constraints has %d values for %d columns", static_cast<int>(cfg_.monotone_constraints.size()), ds_->num_total_features);
+    LGB_CHECK(cfg_.monotone_penalty >= 0.0, "monotone_penalty must not be negative");
+    std::vector<signed char> mono(std::max(F_, 1), 0);
+    for (int f = 0; f < F_; ++f) {
+      const int v = cfg_.monotone_constraints[ds_->used[f]];
+      LGB_CHECK(v >= -1 && v <= 1, "monotone_constraints values must be -1, 0 or 1");
+      LGB_CHECK(v == 0 || ds_->mappers[ds_->used[f]].bin_type == 0, "a categorical feature cannot carry a monotone constraint");
+      mono[f] = static_cast<signed char>(v);
+    }
+    d_monotone_.Alloc(mono.size());
+    LGB_CUDA(cudaMemcpy(d_monotone_.p, mono.data(), mono.size(), cudaMemcpyHostToDevice));
+    lp_.monotone = d_monotone_.p;
+    find_warp_ = false;      // the constrained search exists in the CTA form only
+  }
   lp_.feature_mask = nullptr;
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
@@ -688,12 +709,13 @@ void Booster::LaunchFind(bool root) {
   // narrow data: a 256-thread CTA per (feature, child, batch item) — a few hundred CTAs, lowest latency; wide data: a warp per unit
   if (!find_warp_) {
     dim3 grid(funits, root ? 1 : 2, root ? 1 : max_batch_);
-    if (lp_.quantized)
-      LaunchPdl(k_bt_find<true>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
-    else
-      LaunchPdl(k_bt_find<false>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_,
-                d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt);
+    // (the second template flag compiles the categorical / wide-feature / constrained search in or out: batch_tree.cuh)
+    const bool ext = ds_->has_categorical || ds_->has_wide || lp_.monotone != nullptr;
+#define LGB_FIND(Q, E) LaunchPdl(k_bt_find<Q, E>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_, \
+                                 d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt)
+    if (lp_.quantized) { if (ext) LGB_FIND(true, true); else LGB_FIND(true, false); }
+    else { if (ext) LGB_FIND(false, true); else LGB_FIND(false, false); }
+#undef LGB_FIND
   } else {
     dim3 grid(CeilDiv(funits, kFindWarps), root ? 1 : 2, root ? 1 : max_batch_);
     if (lp_.quantized)

@@ -30,7 +30,8 @@ struct SplitDev {
   int missing_type, nan_bin;   // of the split feature (nan_bin = -1: none), so that later stages need no feature table lookup
   // categorical split: the rows whose bin has its bit set in cat_bits go left, everything else (bin 0 included) right; threshold,
   // default_left and nan_bin are unused
-  int is_cat, pad_;
+  int is_cat;
+  int monotone_type;           // direction of the split feature (monotone constraints; 0 for categorical splits)
   unsigned int cat_bits[8];
 };
 
@@ -109,6 +110,10 @@ struct LearnerParams {
   // categorical split search (upstream config.h: max_cat_to_onehot, max_cat_threshold, min_data_per_group, cat_smooth, cat_l2)
   int max_cat_to_onehot, max_cat_threshold, min_data_per_group;
   double cat_smooth, cat_l2;
+  // monotone constraints, method "basic": per column +1 / -1 / 0, nullptr when no column is constrained (then nothing changes:
+  // upstream's USE_MC code path — gains taken at clamped outputs — is on for EVERY feature as soon as one column is constrained)
+  const signed char* monotone;
+  double monotone_penalty;
 };
 
 class Booster {
@@ -277,6 +282,7 @@ class Booster {
   DevBuf<SplitDev> d_feat_best_;     // [2][F]
   DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
   DevBuf<unsigned char> d_feature_mask_; // [F] this tree's column sample (feature_fraction < 1 only)
+  DevBuf<signed char> d_monotone_;       // [F] monotone direction per column (only with monotone_constraints)
   HostRandom feature_rand_{2};           // ColSampler's stream, seeded with feature_fraction_seed
   void SampleFeaturesForTree();
   bool TrainOneIter(const float* grad, const float* hess);

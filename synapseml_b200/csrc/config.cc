@@ -60,6 +60,9 @@ std::string Config::CanonicalKey(const std::string& k) {
       {"sub_feature_bynode", "feature_fraction_bynode"}, {"colsample_bynode", "feature_fraction_bynode"},
       {"sub_row", "bagging_fraction"}, {"subsample", "bagging_fraction"}, {"bagging", "bagging_fraction"},
       {"subsample_freq", "bagging_freq"}, {"bagging_fraction_seed", "bagging_seed"},
+      {"mc", "monotone_constraints"}, {"monotone_constraint", "monotone_constraints"}, {"monotonic_cst", "monotone_constraints"},
+      {"monotone_constraining_method", "monotone_constraints_method"}, {"mc_method", "monotone_constraints_method"},
+      {"monotone_splits_penalty", "monotone_penalty"}, {"ms_penalty", "monotone_penalty"}, {"mc_penalty", "monotone_penalty"},
       {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"},
       {"cat_column", "categorical_feature"}, {"categorical_features", "categorical_feature"},
   };
@@ -139,6 +142,9 @@ void Config::Set(const std::string& params) {
   if (has("eval_at")) eval_at = ToList<int>("eval_at", kv["eval_at"]);
   if (has("categorical_feature")) categorical_feature = ToList<int>("categorical_feature", kv["categorical_feature"]);
   if (has("max_bin_by_feature")) max_bin_by_feature = ToList<int>("max_bin_by_feature", kv["max_bin_by_feature"]);
+  if (has("monotone_constraints")) monotone_constraints = ToList<int>("monotone_constraints", kv["monotone_constraints"]);
+  if (has("monotone_constraints_method")) monotone_constraints_method = kv["monotone_constraints_method"];
+  GET_D(monotone_penalty);
   GET_I(max_cat_to_onehot); GET_I(max_cat_threshold); GET_I(min_data_per_group); GET_D(cat_smooth); GET_D(cat_l2);
 #undef GET_I
 #undef GET_D

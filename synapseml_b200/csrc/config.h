@@ -69,6 +69,9 @@ struct Config {
   // knobs of the categorical split search (upstream config.h defaults; CategoricalParams in params/TrainParams.scala)
   std::vector<int> categorical_feature;
   std::vector<int> max_bin_by_feature;      // one max_bin per column (dataset construction only, as upstream)
+  std::vector<int> monotone_constraints;    // per column: +1 increasing, -1 decreasing, 0 free (LightGBMParams.scala monotoneConstraints)
+  std::string monotone_constraints_method = "basic";
+  double monotone_penalty = 0.0;
   int max_cat_to_onehot = 4, max_cat_threshold = 32, min_data_per_group = 100;
   double cat_smooth = 10.0, cat_l2 = 10.0;
   std::map<std::string, std::string> raw;   // canonical key -> value as received (echoed into the model's parameters block)

@@ -412,6 +412,33 @@ __device__ __forceinline__ double SplitGainD(double lg, double lh, double rg, do
   return LeafGainD(lg, lh, p) + LeafGainD(rg, rh, p);
 }
 
+// Monotone constraints, method "basic" (upstream monotone_constraints.hpp BasicLeafConstraints, feature_histogram.hpp USE_MC): a leaf
+// carries an output range [cmin, cmax]; while any column is constrained, every candidate's gain is taken at the children's outputs
+// clamped to that range (GetLeafGainGivenOutput), a split that breaks the searched feature's direction has gain 0, and the outputs
+// handed on are the clamped ones.
+struct McCtx { int on; int mono; double cmin, cmax; };
+__device__ __forceinline__ double LeafGainGivenOutputD(double g, double h, const LearnerParams& p, double out) {
+  const double sg = (p.l1 > 0.0) ? ThresholdL1D(g, p.l1) : g;
+  return -(2.0 * sg * out + (h + p.l2) * out * out);
+}
+__device__ __forceinline__ double LeafOutputX(double g, double h, const LearnerParams& p, const McCtx& mc) {
+  double ret = LeafOutputD(g, h, p);
+  if (mc.on) { if (ret < mc.cmin) ret = mc.cmin; else if (ret > mc.cmax) ret = mc.cmax; }
+  return ret;
+}
+__device__ __forceinline__ double SplitGainX(double lg, double lh, double rg, double rh, const LearnerParams& p, const McCtx& mc) {
+  if (!mc.on) return LeafGainD(lg, lh, p) + LeafGainD(rg, rh, p);
+  const double lo = LeafOutputX(lg, lh, p, mc), ro = LeafOutputX(rg, rh, p, mc);
+  if ((mc.mono > 0 && lo > ro) || (mc.mono < 0 && lo < ro)) return 0.0;
+  return LeafGainGivenOutputD(lg, lh, p, lo) + LeafGainGivenOutputD(rg, rh, p, ro);
+}
+// LeafConstraintsBase::ComputeMonotoneSplitGainPenalty: the factor on the gain of a split on a constrained feature at this depth
+__device__ __forceinline__ double MonotonePenaltyD(int depth, double penalization) {
+  if (penalization >= depth + 1.) return KEPS;
+  if (penalization <= 1.) return 1. - penalization / pow(2., static_cast<double>(depth)) + KEPS;
+  return 1. - pow(2., penalization - 1. - depth) + KEPS;
+}
+
 __device__ __forceinline__ bool SplitBetter(double ga, int fa, double gb, int fb) {
   // upstream SplitInfo::operator>: larger gain; equal gain -> smaller real feature index (-1 = +inf)
   const int a = fa < 0 ? 0x7fffffff : fa, b = fb < 0 ? 0x7fffffff : fb;
@@ -426,7 +453,7 @@ __device__ __forceinline__ SplitDev EmptySplit(int f, int real) {
   s.left_sum_g = s.left_sum_h = s.right_sum_g = s.right_sum_h = 0.0;
   s.left_int_g = s.left_int_h = s.right_int_g = s.right_int_h = 0;
   s.missing_type = 0; s.nan_bin = -1;
-  s.is_cat = 0; s.pad_ = 0;
+  s.is_cat = 0; s.monotone_type = 0;
   #pragma unroll
   for (int i = 0; i < 8; ++i) s.cat_bits[i] = 0u;
   return s;
@@ -468,11 +495,11 @@ __device__ __forceinline__ Cand BlockBestCand(Cand c, bool prefer_larger_b, Cand
 // ...Int (reverse scan, plus a forward scan when the feature has a NaN bin and more than two bins) with block-wide prefix
 // sums: the sequential `continue` / `break` conditions are monotone in the scan position, so they become per-threshold
 // predicates.  g_in/h_in: this thread's bin of the leaf's histogram.  Result valid in thread 0.
-template <bool QUANT>
+template <bool QUANT, bool MC = false>
 __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
                               long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
                               double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
-                              long long* out_tot_g, long long* out_tot_h, int sub) {
+                              long long* out_tot_g, long long* out_tot_h, int sub, const McCtx mc = McCtx{0, 0, 0.0, 0.0}, int depth = 0) {
   __shared__ long long s_g_all[kMaxFindSubs][8], s_h_all[kMaxFindSubs][8];
   __shared__ int s_c_all[kMaxFindSubs][8];
   __shared__ Cand s_cand_all[kMaxFindSubs][8];
@@ -552,14 +579,14 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
       const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
       const double slh = static_cast<double>(lhi) * hscale;
       ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
-      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      if (ok) gain = (MC ? SplitGainX(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P, mc) : SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P));
     } else {
       rc = Tc - (pc - cv);
       const double rh = KEPS + static_cast<double>(rhi) * hscale;
       const int lc = num_data - rc;
       const double lh = sum_hessian - rh;
       ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
-      if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
+      if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = (MC ? SplitGainX(sum_gradient - rg, lh, rg, rh, P, mc) : SplitGainD(sum_gradient - rg, lh, rg, rh, P)); }
     }
     if (ok && gain > min_gain_shift) { splittable = true; cr.gain = gain; cr.b = b; cr.sg = rgi; cr.sh = rhi; cr.cnt = rc; }
   }
@@ -575,14 +602,14 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
       const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
       const double srh = static_cast<double>(rhi) * hscale;
       ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
-      if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+      if (ok) gain = (MC ? SplitGainX(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P, mc) : SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P));
     } else {
       lc = pc - (fstart ? s_c0_all[sub] : 0);
       const double lh = KEPS + static_cast<double>(lhi) * hscale;
       const int rc = num_data - lc;
       const double rh = sum_hessian - lh;
       ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
-      if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
+      if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = (MC ? SplitGainX(lg, lh, sum_gradient - lg, rh, P, mc) : SplitGainD(lg, lh, sum_gradient - lg, rh, P)); }
     }
     if (ok && gain > min_gain_shift) { splittable = true; cf.gain = gain; cf.b = b; cf.sg = lgi; cf.sh = lhi; cf.cnt = lc; }
   }
@@ -593,13 +620,14 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
   SubSync(sub);
   if (b == 0) {
     const bool any = s_flag != 0;
+    const bool accept = !(MC && mc.cmin > mc.cmax);      // an empty output range accepts no candidate (the feature stays "splittable")
     SplitDev s = EmptySplit(f, fm.real_index);
     s.missing_type = fm.missing_type;
     s.nan_bin = (fm.missing_type == kMissingNaN) ? fm.num_bin - 1 : zero_type ? fm.default_bin : -1;      // rows of this bin follow default_left
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;
-      if (!(any && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      if (!(any && accept && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
       const bool reverse = pass == 0;
       if (QUANT) {
         const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
@@ -607,10 +635,10 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
         const double blg = static_cast<double>(lgi) * gscale, blh = static_cast<double>(lhi) * hscale;
         const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
         s.threshold = reverse ? c.b - 1 : c.b;
-        s.left_output = LeafOutputD(blg, blh, P);
+        s.left_output = (MC ? LeafOutputX(blg, blh, P, mc) : LeafOutputD(blg, blh, P));
         s.left_count = RoundIntD(static_cast<double>(lhi) * cnt_factor);
         s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = lgi; s.left_int_h = lhi;
-        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_output = (MC ? LeafOutputX(brg, brh, P, mc) : LeafOutputD(brg, brh, P));
         s.right_count = RoundIntD(static_cast<double>(rhi) * cnt_factor);
         s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
       } else {
@@ -622,10 +650,10 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
           best_lg = static_cast<double>(c.sg) * gscale; best_lh = KEPS + static_cast<double>(c.sh) * hscale; left_count = c.cnt;
         }
         s.threshold = reverse ? c.b - 1 : c.b;
-        s.left_output = LeafOutputD(best_lg, best_lh, P);
+        s.left_output = (MC ? LeafOutputX(best_lg, best_lh, P, mc) : LeafOutputD(best_lg, best_lh, P));
         s.left_count = left_count;
         s.left_sum_g = best_lg; s.left_sum_h = best_lh - KEPS;
-        s.right_output = LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P);
+        s.right_output = (MC ? LeafOutputX(sum_gradient - best_lg, sum_hessian - best_lh, P, mc) : LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P));
         s.right_count = num_data - left_count;
         s.right_sum_g = sum_gradient - best_lg; s.right_sum_h = sum_hessian - best_lh - KEPS;
       }
@@ -633,6 +661,7 @@ __device__ void BlockFindBest(long long g_in, long long h_in, const FeatureMetaD
       s.default_left = reverse ? 1 : 0;
     }
     if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    if (MC && mc.mono != 0) { s.monotone_type = mc.mono; s.gain *= MonotonePenaltyD(depth, P.monotone_penalty); }
     *out = s;
     *splittable_out = any ? 1 : 0;
   }
@@ -656,7 +685,7 @@ template <bool QUANT>
 __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMetaDev fm, int f, bool root, long long tot_g,
                                  long long tot_h, double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P,
                                  double gscale, double hscale, SplitDev* out, unsigned char* splittable_out,
-                                 long long* out_tot_g, long long* out_tot_h, int sub) {
+                                 long long* out_tot_g, long long* out_tot_h, int sub, const McCtx mc = McCtx{0, 0, 0.0, 0.0}, int depth = 0) {
   __shared__ long long s_g[8], s_h[8];
   __shared__ double s_key[kFindThreads];
   __shared__ long long s_bg[kFindThreads], s_bh[kFindThreads];
@@ -712,7 +741,7 @@ __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMe
       else { soh = sum_hessian - hess - KEPS; sog = sum_gradient - grad; }
       ok = ok && !(soh < P.min_sum_hessian);
       if (ok) {
-        const double gain = SplitGainD(sog, soh, grad, hess + eps, P);
+        const double gain = SplitGainX(sog, soh, grad, hess + eps, P, mc);
         if (gain > min_gain_shift) { c.gain = gain; c.b = b; c.sg = g_in; c.sh = h_in; c.cnt = cnt; }
       }
     }
@@ -721,16 +750,16 @@ __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMe
       any = true;
       const double blg = static_cast<double>(best.sg) * gscale, blh = static_cast<double>(best.sh) * hscale + eps;
       s.left_count = best.cnt; s.right_count = num_data - best.cnt;
-      s.left_output = LeafOutputD(blg, blh, P);
+      s.left_output = LeafOutputX(blg, blh, P, mc);
       if (QUANT) {
         const long long rgi = tot_g - best.sg, rhi = tot_h - best.sh;
         const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
         s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = best.sg; s.left_int_h = best.sh;
-        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_output = LeafOutputX(brg, brh, P, mc);
         s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
       } else {
         s.left_sum_g = blg; s.left_sum_h = blh - KEPS;
-        s.right_output = LeafOutputD(sum_gradient - blg, sum_hessian - blh, P);
+        s.right_output = LeafOutputX(sum_gradient - blg, sum_hessian - blh, P, mc);
         s.right_sum_g = sum_gradient - blg; s.right_sum_h = sum_hessian - blh - KEPS;
       }
       s.gain = best.gain - min_gain_shift;
@@ -791,7 +820,7 @@ __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMe
         if (cnt_cur_group < P.min_data_per_group) continue;
         cnt_cur_group = 0;
         const double sum_right_gradient = QUANT ? static_cast<double>(tot_g - ilg) * gscale : sum_gradient - sum_left_gradient;
-        const double gain = SplitGainD(sum_left_gradient, sum_left_hessian, sum_right_gradient, sum_right_hessian, Pc);
+        const double gain = SplitGainX(sum_left_gradient, sum_left_hessian, sum_right_gradient, sum_right_hessian, Pc, mc);
         if (gain <= min_gain_shift) continue;
         if (gain > best.gain) {
           best.gain = gain; best.thr = i; best.left_count = left_count; best.ig = ilg; best.ih = ilh;
@@ -809,16 +838,16 @@ __device__ void BlockFindBestCat(long long g_in, long long h_in, const FeatureMe
       if (best.thr >= 0) {
         any = true;
         s.left_count = best.left_count; s.right_count = num_data - best.left_count;
-        s.left_output = LeafOutputD(best.lg, best.lh, Pc);
+        s.left_output = LeafOutputX(best.lg, best.lh, Pc, mc);
         if (QUANT) {
           const long long rgi = tot_g - best.ig, rhi = tot_h - best.ih;
           const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
           s.left_sum_g = best.lg; s.left_sum_h = best.lh; s.left_int_g = best.ig; s.left_int_h = best.ih;
-          s.right_output = LeafOutputD(brg, brh, Pc);
+          s.right_output = LeafOutputX(brg, brh, Pc, mc);
           s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
         } else {
           s.left_sum_g = best.lg; s.left_sum_h = best.lh - KEPS;
-          s.right_output = LeafOutputD(sum_gradient - best.lg, sum_hessian - best.lh, Pc);
+          s.right_output = LeafOutputX(sum_gradient - best.lg, sum_hessian - best.lh, Pc, mc);
           s.right_sum_g = sum_gradient - best.lg; s.right_sum_h = sum_hessian - best.lh - KEPS;
         }
         s.gain = best.gain - min_gain_shift;
@@ -856,7 +885,7 @@ template <bool QUANT, typename Load>
 __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f, bool root, long long tot_g, long long tot_h,
                                   double leaf_sum_g, double leaf_sum_h, int num_data, const LearnerParams& P, double gscale,
                                   double hscale, SplitDev* out, unsigned char* splittable_out, long long* out_tot_g,
-                                  long long* out_tot_h, const long long* slot, int sub) {
+                                  long long* out_tot_h, const long long* slot, int sub, const McCtx mc = McCtx{0, 0, 0.0, 0.0}, int depth = 0) {
   __shared__ long long s_g[8], s_h[8];
   __shared__ int s_c[8];
   __shared__ Cand s_cand[8];
@@ -975,14 +1004,14 @@ __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f
         const long long lgi = tot_g - rgi, lhi = tot_h - rhi;
         const double slh = static_cast<double>(lhi) * hscale;
         ok = !(rc < P.min_data_in_leaf || srh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(slh < P.min_sum_hessian);
-        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+        if (ok) gain = SplitGainX(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P, mc);
       } else {
         rc = Tc - (pc - cv);
         const double rh = KEPS + static_cast<double>(rhi) * hscale;
         const int lc = num_data - rc;
         const double lh = sum_hessian - rh;
         ok = !(rc < P.min_data_in_leaf || rh < P.min_sum_hessian) && !(lc < P.min_data_in_leaf) && !(lh < P.min_sum_hessian);
-        if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainD(sum_gradient - rg, lh, rg, rh, P); }
+        if (ok) { const double rg = static_cast<double>(rgi) * gscale; gain = SplitGainX(sum_gradient - rg, lh, rg, rh, P, mc); }
       }
       if (ok && gain > min_gain_shift) {
         splittable = true;
@@ -1000,14 +1029,14 @@ __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f
         const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
         const double srh = static_cast<double>(rhi) * hscale;
         ok = !(lc < P.min_data_in_leaf || slh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(srh < P.min_sum_hessian);
-        if (ok) gain = SplitGainD(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P);
+        if (ok) gain = SplitGainX(static_cast<double>(lgi) * gscale, slh, static_cast<double>(rgi) * gscale, srh, P, mc);
       } else {
         lc = pc - (fstart ? c0 : 0);
         const double lh = KEPS + static_cast<double>(lhi) * hscale;
         const int rc = num_data - lc;
         const double rh = sum_hessian - lh;
         ok = !(lc < P.min_data_in_leaf || lh < P.min_sum_hessian) && !(rc < P.min_data_in_leaf) && !(rh < P.min_sum_hessian);
-        if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainD(lg, lh, sum_gradient - lg, rh, P); }
+        if (ok) { const double lg = static_cast<double>(lgi) * gscale; gain = SplitGainX(lg, lh, sum_gradient - lg, rh, P, mc); }
       }
       if (ok && gain > min_gain_shift) {
         splittable = true;
@@ -1023,23 +1052,24 @@ __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f
   SubSync(sub);
   if (b == 0) {
     const bool any = s_flag != 0;
+    const bool accept = !(mc.on && mc.cmin > mc.cmax);      // an empty output range accepts no candidate (the feature stays "splittable")
     SplitDev s = EmptySplit(f, fm.real_index);
     s.missing_type = fm.missing_type;
     int thr = 0;
     for (int pass = 0; pass < 2; ++pass) {
       const Cand& c = pass == 0 ? best_r : best_f;
       if (pass == 1 && !two_scans) break;
-      if (!(any && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
+      if (!(any && accept && c.b >= 0 && c.gain > s.gain + min_gain_shift)) continue;
       const bool reverse = pass == 0;
       if (QUANT) {
         const long long lgi = reverse ? tot_g - c.sg : c.sg, lhi = reverse ? tot_h - c.sh : c.sh;
         const long long rgi = tot_g - lgi, rhi = tot_h - lhi;
         const double blg = static_cast<double>(lgi) * gscale, blh = static_cast<double>(lhi) * hscale;
         const double brg = static_cast<double>(rgi) * gscale, brh = static_cast<double>(rhi) * hscale;
-        s.left_output = LeafOutputD(blg, blh, P);
+        s.left_output = LeafOutputX(blg, blh, P, mc);
         s.left_count = RoundIntD(static_cast<double>(lhi) * cnt_factor);
         s.left_sum_g = blg; s.left_sum_h = blh; s.left_int_g = lgi; s.left_int_h = lhi;
-        s.right_output = LeafOutputD(brg, brh, P);
+        s.right_output = LeafOutputX(brg, brh, P, mc);
         s.right_count = RoundIntD(static_cast<double>(rhi) * cnt_factor);
         s.right_sum_g = brg; s.right_sum_h = brh; s.right_int_g = rgi; s.right_int_h = rhi;
       } else {
@@ -1050,10 +1080,10 @@ __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f
         } else {
           best_lg = static_cast<double>(c.sg) * gscale; best_lh = KEPS + static_cast<double>(c.sh) * hscale; left_count = c.cnt;
         }
-        s.left_output = LeafOutputD(best_lg, best_lh, P);
+        s.left_output = LeafOutputX(best_lg, best_lh, P, mc);
         s.left_count = left_count;
         s.left_sum_g = best_lg; s.left_sum_h = best_lh - KEPS;
-        s.right_output = LeafOutputD(sum_gradient - best_lg, sum_hessian - best_lh, P);
+        s.right_output = LeafOutputX(sum_gradient - best_lg, sum_hessian - best_lh, P, mc);
         s.right_count = num_data - left_count;
         s.right_sum_g = sum_gradient - best_lg; s.right_sum_h = sum_hessian - best_lh - KEPS;
       }
@@ -1062,6 +1092,7 @@ __device__ void BlockFindBestWide(Load child_bin, const FeatureMetaDev fm, int f
       s.default_left = reverse ? 1 : 0;
     }
     if (!two_scans && fm.missing_type == kMissingNaN) s.default_left = 0;
+    if (mc.on && mc.mono != 0) { s.monotone_type = mc.mono; s.gain *= MonotonePenaltyD(depth, P.monotone_penalty); }
     // column form: the split's column, the byte threshold in it, and the byte whose rows follow default_left there
     const int ct = thr / kWideLocalBins;
     const int miss = fm.missing_type == kMissingNaN ? NB - 1 : zero_type ? fm.default_bin : -1;

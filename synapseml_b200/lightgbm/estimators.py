@@ -73,6 +73,7 @@ _DEFAULTS = dict(
     # categorical features (LightGBMParams.scala:286-296, 451-483): slot indexes and / or slot names (resolved against slotNames)
     categoricalSlotIndexes=None, categoricalSlotNames=None, minDataPerGroup=None, maxCatThreshold=None, catl2=None, catSmooth=None,
     maxCatToOnehot=None,
+    monotoneConstraints=None, monotoneConstraintsMethod=None, monotonePenalty=None,      # LightGBMParams.scala (method "basic" is built)
     maxBinByFeature=None,      # LightGBMParams.scala: sent with the TRAIN parameters only (LightGBMBase.scala:374-386 leaves it out of the
                                # dataset parameters), where the native side can only warn that the dataset is already built — as with lightgbmlib
     fobj=None,      # FObjTrait: an object with get_gradient(predictions [n][1], training_dataset) -> (grad f32[n], hess f32[n])
@@ -134,7 +135,8 @@ class LightGBMBase:
     # ------------------------------------------------------------------ param groups (LightGBMBase.scala:240-372)
     def _general_params(self, num_tasks):
         g = self._p
-        return GeneralParams(categoricalFeatures=self.get_categorical_indexes(), maxBinByFeature=list(g["maxBinByFeature"] or []), parallelism=g["parallelism"], topK=g["topK"], numIterations=g["numIterations"], learningRate=g["learningRate"],
+        return GeneralParams(categoricalFeatures=self.get_categorical_indexes(), maxBinByFeature=list(g["maxBinByFeature"] or []), monotoneConstraints=list(g["monotoneConstraints"] or []),
+                             monotoneConstraintsMethod=g["monotoneConstraintsMethod"], monotonePenalty=g["monotonePenalty"], parallelism=g["parallelism"], topK=g["topK"], numIterations=g["numIterations"], learningRate=g["learningRate"],
                              numLeaves=g["numLeaves"], maxBin=g["maxBin"], binSampleCount=g["binSampleCount"],
                              baggingFraction=g["baggingFraction"], posBaggingFraction=g["posBaggingFraction"],
                              negBaggingFraction=g["negBaggingFraction"], baggingFreq=g["baggingFreq"], baggingSeed=g["baggingSeed"],

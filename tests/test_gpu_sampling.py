@@ -76,7 +76,7 @@ def test_unimplemented_sampling_modes_are_refused(native):
     X, y = S.higgs_shape(5000)
     base = "objective=binary num_leaves=7 max_bin=63 verbosity=-1 "
     nd = NativeDataset(X, y, base)
-    for extra in ("feature_fraction_bynode=0.5", "bagging_freq=1 pos_bagging_fraction=1.5", "monotone_constraints=1,0,-1",
+    for extra in ("feature_fraction_bynode=0.5", "bagging_freq=1 pos_bagging_fraction=1.5", "monotone_constraints=1,0,-1 monotone_constraints_method=advanced",
                   "extra_trees=true", "feature_fraction=0"):
         with pytest.raises(Exception):
             NativeBooster(nd, base + extra)
