@@ -74,6 +74,18 @@ _DEFAULTS = dict(
     categoricalSlotIndexes=None, categoricalSlotNames=None, minDataPerGroup=None, maxCatThreshold=None, catl2=None, catSmooth=None,
     maxCatToOnehot=None,
     monotoneConstraints=None, monotoneConstraintsMethod=None, monotonePenalty=None,      # LightGBMParams.scala (method "basic" is built)
+    # DART (LightGBMDartParams) and the remaining seeds (LightGBMSeedParams)
+    dropRate=0.1, maxDrop=50, skipDrop=0.5, xGBoostDartMode=False, uniformDrop=False,
+    featureFractionSeed=None, extraSeed=None, dropSeed=None, objectiveSeed=None,
+    # numBatches > 0: the rows are split into that many random batches which are trained one after the other, every batch continuing
+    # from the model of the one before it (LightGBMBase.scala:39-64)
+    numBatches=0,
+    # model output columns (LightGBMPredictionParams): empty = not produced; startIteration: first iteration used for prediction
+    leafPredictionCol="", featuresShapCol="", startIteration=0, predictDisableShapeCheck=False,
+    maxNumClasses=100,      # LightGBMClassifier: more label values than this is taken for a regression problem and refused
+    # Spark-only controls, accepted and without effect here (one process per GPU, launched by torchrun: no Spark tasks to cap,
+    # barrier or repartition, no driver socket)
+    numTasks=0, useBarrierExecutionMode=False, repartitionByGroupingColumn=True, driverListenPort=0,
     maxBinByFeature=None,      # LightGBMParams.scala: sent with the TRAIN parameters only (LightGBMBase.scala:374-386 leaves it out of the
                                # dataset parameters), where the native side can only warn that the dataset is already built — as with lightgbmlib
     fobj=None,      # FObjTrait: an object with get_gradient(predictions [n][1], training_dataset) -> (grad f32[n], hess f32[n])
@@ -155,11 +167,13 @@ class LightGBMBase:
             passThroughArgs=g["passThroughArgs"], isProvideTrainingMetric=g["isProvideTrainingMetric"], delegate=g["delegate"],
             generalParams=self._general_params(num_tasks),
             datasetParams=DatasetParams(g["isEnableSparse"], g["useMissing"], g["zeroAsMissing"]),
-            dartModeParams=DartModeParams(),
+            dartModeParams=DartModeParams(g["dropRate"], g["maxDrop"], g["skipDrop"], g["xGBoostDartMode"], g["uniformDrop"]),
             executionParams=ExecutionParams(g["chunkSize"], g["matrixType"], exec_threads, g["dataTransferMode"], g["samplingMode"],
                                             g["samplingSubsetSize"], g["microBatchSize"], g["useSingleDatasetMode"], g["maxStreamingOMPThreads"]),
             objectiveParams=ObjectiveParams(g["objective"], g["fobj"]),
             seedParams=SeedParams(seed=g["seed"], deterministic=g["deterministic"], dataRandomSeed=g["dataRandomSeed"],
+                                  baggingSeed=g["baggingSeed"], featureFractionSeed=g["featureFractionSeed"], extraSeed=g["extraSeed"],
+                                  dropSeed=g["dropSeed"], objectiveSeed=g["objectiveSeed"],
                                   boostingType=g["boostingType"], objective=g["objective"]),
             categoricalParams=CategoricalParams(g["minDataPerGroup"], g["maxCatThreshold"], g["catl2"], g["catSmooth"], g["maxCatToOnehot"]),
             quantizedParams=QuantizedGradParams(g["useQuantizedGrad"], g["numGradQuantBins"], g["stochasticRounding"]))
@@ -233,7 +247,30 @@ class LightGBMBase:
 
     # ------------------------------------------------------------------ train
     def fit(self, df):
-        """LightGBMBase.train -> trainOneDataBatch: row statistics, bin sample -> reference dataset, then the partition task."""
+        """LightGBMBase.train (LightGBMBase.scala:33-65): one data batch, or numBatches random batches trained in sequence, each
+        continuing from the model string of the previous one."""
+        nb = int(self._p.get("numBatches") or 0)
+        if nb <= 0:
+            return self._train_one_data_batch(df)
+        # dataset.randomSplit(equal weights): every row draws its batch (Spark's split is seeded at random; here by `seed`)
+        rng = np.random.Generator(np.random.PCG64(self._p["seed"] if self._p["seed"] is not None else 0))
+        draws = [rng.integers(0, nb, len(p["label"])) for p in df.partitions]
+        saved = self._p["modelString"]
+        model = None
+        self.batch_performance_measures = []
+        try:
+            for b in range(nb):
+                parts = [{k: v[d == b] for k, v in p.items()} for p, d in zip(df.partitions, draws)]
+                if model is not None:
+                    self._p["modelString"] = model.getNativeModel()
+                model = self._train_one_data_batch(LocalDataFrame(parts))
+                self.batch_performance_measures.append(self.performance_measures)
+        finally:
+            self._p["modelString"] = saved
+        return model
+
+    def _train_one_data_batch(self, df):
+        """trainOneDataBatch: row statistics, bin sample -> reference dataset, then the partition task."""
         import time
         import torch.distributed as dist
         g = self._p
@@ -301,6 +338,8 @@ class LightGBMBase:
             model_str = payload[0]
         model = self._make_model(model_str)
         model.best_iteration = self.best_iteration
+        model.leafPredictionCol, model.featuresShapCol = g["leafPredictionCol"], g["featuresShapCol"]
+        model.startIteration = g["startIteration"]
         return model
 
     def add_custom_train_params(self, train_params, df, dist):
@@ -322,6 +361,31 @@ class LightGBMModelBase:
         self.model_str = model_str
         self._model = TextModel(model_str)       # parsed text: feature importances only
         self._booster = None
+        # LightGBMPredictionParams: optional output columns of transform, and the first iteration used for prediction
+        self.leafPredictionCol, self.featuresShapCol, self.startIteration = "", "", 0
+
+    def setLeafPredictionCol(self, v):
+        self.leafPredictionCol = v
+        return self
+
+    def setFeaturesShapCol(self, v):
+        self.featuresShapCol = v
+        return self
+
+    def setStartIteration(self, v):
+        self.startIteration = int(v)
+        return self
+
+    def _extra_columns(self, features, out):
+        """The leaf-index and SHAP columns transform adds when their names are set (LightGBMClassifier.scala:151-160)."""
+        if self.leafPredictionCol:
+            out[self.leafPredictionCol] = self.predict_leaf(features)
+        if self.featuresShapCol:
+            out[self.featuresShapCol] = self.predict_contrib(features)
+        return out
+
+    def _predict(self, features, predict_type):
+        return self._native().predict_for_mat(features, predict_type, start_iteration=self.startIteration)
 
     def _native(self):
         if self._booster is None:
@@ -344,18 +408,18 @@ class LightGBMModelBase:
 
     def predict_raw(self, features):
         """Raw scores: [n], or [n, num_class] for a multiclass model."""
-        raw = self._native().predict_for_mat(features, LightGBMBooster.PREDICT_RAW)
+        raw = self._predict(features, LightGBMBooster.PREDICT_RAW)
         K = self._model.num_tree_per_iteration
         return raw if K == 1 else raw.reshape(-1, K)
 
     def predict_leaf(self, features):
-        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
+        return self._predict(features, LightGBMBooster.PREDICT_LEAF).astype(np.int64)
 
     def predict_contrib(self, features):
         """featuresShapCol (LightGBMBooster.scala:418-427, predict type C_API_PREDICT_CONTRIB): per row, the TreeSHAP contribution of
         every feature followed by the expected value — [n, numFeatures + 1], or [n, numClasses * (numFeatures + 1)] for multiclass.
         A row's contributions sum to its raw score."""
-        return self._native().predict_for_mat(features, LightGBMBooster.PREDICT_CONTRIB)
+        return self._predict(features, LightGBMBooster.PREDICT_CONTRIB)
 
     def getFeatureImportances(self, importance_type="split"):
         return self._native().get_feature_importances(importance_type)
@@ -403,24 +467,25 @@ class LightGBMModelBase:
 class LightGBMClassificationModel(LightGBMModelBase):
     def transform(self, features):
         raw = self.predict_raw(features)
-        p = self._native().predict_for_mat(features, LightGBMBooster.PREDICT_NORMAL)
+        p = self._predict(features, LightGBMBooster.PREDICT_NORMAL)
         K = self._model.num_tree_per_iteration
         if K > 1:      # multiclass: one raw score / probability per class (LightGBMBooster.scala:559-575), prediction = arg max
-            return dict(rawPrediction=raw, probability=p.reshape(-1, K), prediction=np.argmax(raw, axis=1).astype(np.float64))
+            return self._extra_columns(features, dict(rawPrediction=raw, probability=p.reshape(-1, K), prediction=np.argmax(raw, axis=1).astype(np.float64)))
         # binary: the native value is the positive-class score; expanded as the reference does (LightGBMBooster.scala:559-575)
-        return dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1), prediction=(p > 0.5).astype(np.float64))
+        return self._extra_columns(features, dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1),
+                                                  prediction=(p > 0.5).astype(np.float64)))
 
 
 class LightGBMRegressionModel(LightGBMModelBase):
     def transform(self, features):
         # LightGBMRegressionModel.predict: score(features, raw = false): the objective's output transform applies (exp for
         # poisson / gamma / tweedie, identity otherwise)
-        return dict(prediction=self._native().predict_for_mat(features, LightGBMBooster.PREDICT_NORMAL))
+        return self._extra_columns(features, dict(prediction=self._predict(features, LightGBMBooster.PREDICT_NORMAL)))
 
 
 class LightGBMRankerModel(LightGBMModelBase):
     def transform(self, features):
-        return dict(prediction=self.predict_raw(features))
+        return self._extra_columns(features, dict(prediction=self.predict_raw(features)))
 
 
 class LightGBMClassifier(LightGBMBase):
@@ -444,6 +509,9 @@ class LightGBMClassifier(LightGBMBase):
             dist.all_gather_object(allmax, local)
             local = max(allmax)
         self._num_class = local + 1
+        if self._num_class > int(self._p["maxNumClasses"]):      # getNumClasses(dataset, maxNumClasses): a label column like that is not categorical
+            raise ValueError("Classifier inferred %d classes from the label column, but at most %d are allowed (maxNumClasses)"
+                             % (self._num_class, int(self._p["maxNumClasses"])))
         train_params.numClass = self._num_class
         return train_params
 

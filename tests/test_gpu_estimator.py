@@ -161,3 +161,32 @@ def test_model_methods(native, tmp_path):
     for again in (LightGBMClassificationModel.loadNativeModelFromFile(str(path)), LightGBMClassificationModel.loadNativeModelFromString(model.getNativeModel())):
         assert again.getNativeModel() == model.getNativeModel()
         assert np.array_equal(again.transform(X[:500])["probability"], model.transform(X[:500])["probability"])
+
+
+def test_dart_seed_batch_and_prediction_params(native):
+    """LightGBMDartParams, the remaining LightGBMSeedParams, numBatches (LightGBMBase.scala:39-64) and LightGBMPredictionParams
+    (leafPredictionCol / featuresShapCol / startIteration)."""
+    X, y = S.higgs_shape(40000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
+    kw = dict(numIterations=10, numLeaves=15, samplingMode="fixed")
+    dart = LightGBMClassifier(boostingType="dart", dropRate=0.4, maxDrop=3, skipDrop=0.1, uniformDrop=True, xGBoostDartMode=True, dropSeed=9,
+                              featureFractionSeed=5, featureFraction=0.8, leafPredictionCol="leaves", featuresShapCol="shap", **kw)
+    model = dart.fit(df)
+    text = model.getNativeModel()
+    for frag in ("[drop_rate: 0.4]", "[max_drop: 3]", "[skip_drop: 0.1]", "[uniform_drop: True]", "[xgboost_dart_mode: True]", "[drop_seed: 9]",
+                 "[feature_fraction_seed: 5]"):
+        assert frag in text, frag
+    out = model.transform(X[:300])
+    assert out["leaves"].shape == (300, 10) and out["shap"].shape == (300, X.shape[1] + 1)
+    assert np.allclose(out["shap"].sum(axis=1), out["rawPrediction"][:, 1], atol=1e-9)
+    # startIteration: the first trees are left out of the prediction
+    late = model.setStartIteration(4).transform(X[:300])
+    assert late["leaves"].shape == (300, 6) and not np.allclose(late["rawPrediction"], out["rawPrediction"])
+    # numBatches: three models trained in sequence, each continuing from the one before: 3 x 10 iterations in the final model
+    batched = LightGBMClassifier(numBatches=3, seed=4, **kw)
+    bm = batched.fit(df)
+    assert bm.getBoosterNumTotalIterations() == 30 and len(batched.batch_performance_measures) == 3
+    from sklearn.metrics import roc_auc_score
+    assert roc_auc_score(y, bm.predict_raw(X)) > roc_auc_score(y, LightGBMClassifier(**kw).fit(df).predict_raw(X)) - 0.01
+    with pytest.raises(ValueError):
+        LightGBMClassifier(objective="multiclass", maxNumClasses=1, **kw).fit(df)
