@@ -180,7 +180,7 @@ struct Config {
   // column / row sampling (upstream config.h defaults); `seed` derives the specific seeds (Config::Set, upstream src/io/config.cpp)
   // regression objectives beyond L2 (upstream config.h defaults)
   double alpha = 0.9, fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;
-  double feature_fraction = 1.0;
+  double feature_fraction = 1.0, feature_fraction_bynode = 1.0;
   int feature_fraction_seed = 2;
   double bagging_fraction = 1.0, pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;
   int bagging_freq = 0, bagging_seed = 3;
@@ -229,6 +229,7 @@ struct Config {
         {"unbalance", "is_unbalance"}, {"unbalanced_sets", "is_unbalance"},
         {"num_thread", "num_threads"}, {"nthread", "num_threads"}, {"nthreads", "num_threads"}, {"n_jobs", "num_threads"},
         {"random_seed", "seed"}, {"random_state", "seed"},
+        {"sub_feature_bynode", "feature_fraction_bynode"}, {"colsample_bynode", "feature_fraction_bynode"},
         {"sub_feature", "feature_fraction"}, {"colsample_bytree", "feature_fraction"},
         {"sub_row", "bagging_fraction"}, {"subsample", "bagging_fraction"}, {"bagging", "bagging_fraction"},
         {"subsample_freq", "bagging_freq"}, {"bagging_fraction_seed", "bagging_seed"},
@@ -322,6 +323,7 @@ struct Config {
     getd("poisson_max_delta_step", &poisson_max_delta_step);
     getd("tweedie_variance_power", &tweedie_variance_power);
     getd("feature_fraction", &feature_fraction);
+    getd("feature_fraction_bynode", &feature_fraction_bynode);
     geti("feature_fraction_seed", &feature_fraction_seed);
     getd("bagging_fraction", &bagging_fraction);
     getd("pos_bagging_fraction", &pos_bagging_fraction); getd("neg_bagging_fraction", &neg_bagging_fraction);

@@ -767,6 +767,20 @@ class Booster {
     for (int f : feature_rand.Sample(F, cnt)) tree_mask[f] = 1;
   }
 
+  // ColSampler::GetByNode (feature_fraction_bynode < 1): a fresh sample for every leaf that is searched, drawn from the tree's own
+  // column sample when there is one, from all used features otherwise — on the same stream as the by-tree sample
+  std::vector<char> SampleFeaturesByNode() {
+    std::vector<char> mask(F, 1);
+    if (!(cfg.feature_fraction_bynode < 1.0)) return mask;
+    std::vector<int> pool;
+    for (int f = 0; f < F; ++f) if (!(cfg.feature_fraction < 1.0) || tree_mask[f]) pool.push_back(f);
+    const int total = static_cast<int>(pool.size());
+    const int cnt = std::max(static_cast<int>(total * cfg.feature_fraction_bynode + 0.5), std::min(2, total));
+    mask.assign(F, 0);
+    for (int i : feature_rand.Sample(total, cnt)) mask[pool[i]] = 1;
+    return mask;
+  }
+
   // ---------------------------------------------------------------- objectives
   void InitObjective() {
     if (cfg.objective == "binary") {
@@ -1263,7 +1277,9 @@ class Booster {
     }
   }
 
-  void FindBestForLeaf(int leaf, const std::vector<char>& used) {
+  // node_mask: the leaf's by-node column sample; a feature outside it is still searched (its splittable flag is recorded) but cannot
+  // be the leaf's split (SerialTreeLearner::ComputeBestSplitForFeature: "new_split > *best_split && is_feature_used")
+  void FindBestForLeaf(int leaf, const std::vector<char>& used, const std::vector<char>* node_mask = nullptr) {
     Leaf& L = leaves[leaf];
     std::vector<SplitInfo> per_feature(F);
     std::vector<char> spl(F, 0);
@@ -1303,6 +1319,7 @@ class Booster {
     for (int f = 0; f < F; ++f) {
       if (!used[f]) { L.splittable[f] = 0; continue; }
       L.splittable[f] = spl[f];
+      if (node_mask != nullptr && !(*node_mask)[f]) continue;
       if (per_feature[f].BetterThan(best)) best = per_feature[f];
     }
     L.best = best;
@@ -1359,8 +1376,9 @@ class Booster {
         if (go) {
           if (right_leaf < 0) {
             std::vector<char> used(tree_mask);
+            const std::vector<char> m0 = SampleFeaturesByNode();
             ConstructHistogram(0, used);
-            FindBestForLeaf(0, used);
+            FindBestForLeaf(0, used, &m0);
           } else {
             int smaller = nl < nr ? left_leaf : right_leaf;
             int larger = nl < nr ? right_leaf : left_leaf;
@@ -1373,8 +1391,9 @@ class Booster {
             const size_t sz = static_cast<size_t>(F) * B * 2;
             if (q) { for (size_t k = 0; k < sz; ++k) hist_i[larger][k] -= hist_i[smaller][k]; }
             else { for (size_t k = 0; k < sz; ++k) hist_f[larger][k] -= hist_f[smaller][k]; }
-            FindBestForLeaf(smaller, used);
-            FindBestForLeaf(larger, used);
+            const std::vector<char> ms = SampleFeaturesByNode(), ml = SampleFeaturesByNode();      // the smaller leaf draws first
+            FindBestForLeaf(smaller, used, &ms);
+            FindBestForLeaf(larger, used, &ml);
           }
         }
       }

@@ -98,7 +98,9 @@ struct BatchCtrl {
   int rounds;
   int applied;             // the finished tree has been added to the scores
   int abort;               // a wait for a peer rank failed: every kernel returns at once, the host raises the error
-  int pad0_;
+  // feature_fraction_bynode: how many by-node column samples the searches of this tree have used so far (the next searched
+  // expansion's children take samples node_draws and node_draws + 1), and whether the last expansion's children were searched
+  int node_draws, last_searched, pad0_;
   unsigned long long part_cursor[kMaxBatch];   // per batch item: (lefts placed << 32) | rights placed
   BatchItem batch[kMaxBatch];
   int find_count[kMaxBatch][2];
@@ -214,7 +216,7 @@ __global__ void k_bt_init(NodeDev* nodes, int* avail, BatchCtrl* ctrl, TreeArray
     nodes[0] = z;
     avail[0] = 0;
     ctrl->num_leaves = 1; ctrl->done = 0; ctrl->num_nodes = 1; ctrl->num_slots = 1; ctrl->batch_n = 0; ctrl->spec_used = 0;
-    ctrl->rounds = 0; ctrl->applied = 0;
+    ctrl->rounds = 0; ctrl->applied = 0; ctrl->node_draws = 0; ctrl->last_searched = 0;
     for (int k = 0; k < kMaxBatch; ++k) { ctrl->find_count[k][0] = 0; ctrl->find_count[k][1] = 0; ctrl->part_cursor[k] = 0ULL; }
   }
 }
@@ -669,6 +671,10 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
   // column sample of this tree (feature_fraction): a feature outside it has no split.  At the root it still runs the search,
   // because the leaf totals come out of it, and its result is discarded.
   const bool sampled = P.feature_mask == nullptr || P.feature_mask[f] != 0;
+  // feature_fraction_bynode (ColSampler::GetByNode): a feature outside the leaf's own sample is searched all the same — its
+  // splittable flag is recorded — but cannot be the leaf's split
+  bool in_node_sample = true;
+  if (EXT && P.node_mask != nullptr) in_node_sample = P.node_mask[static_cast<size_t>(root ? 0 : ctrl->node_draws + c) * F + f] != 0;
   McCtx mc{0, 0, 0.0, 0.0};
   if (EXT && P.monotone != nullptr) { mc.on = 1; mc.mono = fm.bin_type != 0 ? 0 : P.monotone[f]; mc.cmin = me.cmin; mc.cmax = me.cmax; }
   if (EXT && fm.wide_cols < 0) {
@@ -693,6 +699,7 @@ __device__ __forceinline__ void FindUnit(const long long* work, int work_elems, 
                            fb + f, spl, &tg, &th, sub);
     if (!sampled && b == 0) { fb[f] = EmptySplit(f, fm.real_index); *spl = 0; }      // b == 0 wrote the result it now replaces
   }
+  if (EXT && !in_node_sample && b == 0) fb[f] = EmptySplit(f, fm.real_index);      // b == 0 wrote the result it now replaces
   if (P.reduce_in_select && !sliced) {
     // the replay kernel picks the child's best feature (SelectReduceChildren); the first unit publishes everything else
     if (f == 0 && b == 0) {
@@ -1075,6 +1082,14 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
     S.exp = c; c += Lc; S.isleft = c;
   }
   const int tid = threadIdx.x & (kFindThreads - 1);
+  if (P.node_mask != nullptr && tid == 0) {      // the searches that came before this replay used up their by-node samples
+    if (after_root) { ctrl->node_draws = 1; ctrl->last_searched = 1; }
+    else if (ctrl->batch_n > 0) {
+      const int searched = MakeGeom(ctrl->batch[0], ctrl->part_cursor[0], P).find ? 1 : 0;
+      ctrl->last_searched = searched;
+      if (searched) ctrl->node_draws += 2;
+    }
+  }
   const int nl0 = ctrl->num_leaves;
   // the first leaf of every thread: what does not depend on this round's split search is requested before the reduction below,
   // so those round trips overlap it

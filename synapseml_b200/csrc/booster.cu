@@ -73,7 +73,8 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   LGB_CHECK(cfg_.num_grad_quant_bins >= 2 && cfg_.num_grad_quant_bins <= 64, "num_grad_quant_bins=%d is outside [2, 64]", cfg_.num_grad_quant_bins);
   LGB_CHECK(cfg_.feature_fraction > 0.0 && cfg_.feature_fraction <= 1.0, "feature_fraction=%g is outside (0, 1]", cfg_.feature_fraction);
   // parameters that would change the model and are not implemented are refused rather than ignored
-  LGB_CHECK(cfg_.feature_fraction_bynode == 1.0, "feature_fraction_bynode < 1 is not supported by this library yet");
+  LGB_CHECK(cfg_.feature_fraction_bynode > 0.0 && cfg_.feature_fraction_bynode <= 1.0, "feature_fraction_bynode=%g is outside (0, 1]",
+            cfg_.feature_fraction_bynode);
   LGB_CHECK(cfg_.bagging_fraction > 0.0 && cfg_.bagging_fraction <= 1.0, "bagging_fraction=%g is outside (0, 1]", cfg_.bagging_fraction);
   LGB_CHECK(cfg_.pos_bagging_fraction > 0.0 && cfg_.pos_bagging_fraction <= 1.0 && cfg_.neg_bagging_fraction > 0.0 && cfg_.neg_bagging_fraction <= 1.0,
             "pos_bagging_fraction / neg_bagging_fraction must be in (0, 1]");
@@ -153,10 +154,19 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
     find_warp_ = false;      // the constrained search exists in the CTA form only
   }
   lp_.feature_mask = nullptr;
+  feature_rand_ = HostRandom(cfg_.feature_fraction_seed);
   if (cfg_.feature_fraction < 1.0 && F_ > 0) {
     d_feature_mask_.Alloc(F_);
     lp_.feature_mask = d_feature_mask_.p;
-    feature_rand_ = HostRandom(cfg_.feature_fraction_seed);
+  }
+  // feature_fraction_bynode (LightGBMParams.scala featureFractionByNode; ColSampler::GetByNode): every searched leaf draws its own
+  // column sample from one stream, in upstream's sequential order — so leaves are expanded one per round (no speculation), and the
+  // tree's samples are drawn ahead on the host in the order the device will use them
+  lp_.node_mask = nullptr;
+  if (cfg_.feature_fraction_bynode < 1.0 && F_ > 0) {
+    d_node_mask_.Alloc(static_cast<size_t>(1 + 2 * (cfg_.num_leaves - 1)) * F_);
+    lp_.node_mask = d_node_mask_.p;
+    find_warp_ = false;
   }
 
   const int L = cfg_.num_leaves;
@@ -179,6 +189,7 @@ Booster::Booster(Dataset* train, const char* params) : ds_(train) {
   {
     const char* env = getenv("LGB_B200_MAX_BATCH");
     max_batch_ = env ? std::max(1, std::min(kMaxBatch, atoi(env))) : kMaxBatch;
+    if (lp_.node_mask != nullptr) max_batch_ = 1;
   }
   if (const char* env = getenv("LGB_B200_PART_BLOCKS")) part_blocks_ = std::max(1, atoi(env));
   if (const char* env = getenv("LGB_B200_ROUND_SLACK")) round_slack_ = atoi(env);      // experiments
@@ -710,7 +721,7 @@ void Booster::LaunchFind(bool root) {
   if (!find_warp_) {
     dim3 grid(funits, root ? 1 : 2, root ? 1 : max_batch_);
     // (the second template flag compiles the categorical / wide-feature / constrained search in or out: batch_tree.cuh)
-    const bool ext = ds_->has_categorical || ds_->has_wide || lp_.monotone != nullptr;
+    const bool ext = ds_->has_categorical || ds_->has_wide || lp_.monotone != nullptr || lp_.node_mask != nullptr;
 #define LGB_FIND(Q, E) LaunchPdl(k_bt_find<Q, E>, grid, dim3(256), 0, stream_, work, work_elems_, d_hist_pool_.p, ds_->d_fmeta.p, d_nodes_, d_ctrl_, \
                                  d_feat_best_.p, d_splittable_.p, lp_, root ? 1 : 0, pt)
     if (lp_.quantized) { if (ext) LGB_FIND(true, true); else LGB_FIND(true, false); }
@@ -921,11 +932,33 @@ void Booster::SampleFeaturesForTree() {
   const int NF = ds_->num_logical_features();
   const int min_cnt = std::min(2, NF);
   const int cnt = std::max(static_cast<int>(NF * cfg_.feature_fraction + 0.5), min_cnt);
-  std::vector<unsigned char> mask(F_, 0);
+  std::vector<unsigned char>& mask = tree_mask_host_;
+  mask.assign(F_, 0);
   for (int lf : feature_rand_.Sample(NF, cnt))
     for (int c = 0; c < ds_->logical_num_cols[lf]; ++c) mask[ds_->logical_first_col[lf] + c] = 1;
   // pageable source: the runtime stages it before the call returns, so the vector may go out of scope
   LGB_CUDA(cudaMemcpyAsync(d_feature_mask_.p, mask.data(), F_, cudaMemcpyHostToDevice, stream_));
+}
+
+// ColSampler::GetByNode for every search this tree can make (the root, then the smaller and the larger child of every split but
+// the last), drawn from the tree's own column sample when there is one, on the column sampler's stream.  How many of them the tree
+// really used is known when it is finished (FetchTree); the stream is then rewound and advanced by exactly that many draws.
+void Booster::SampleNodeMasksForTree() {
+  std::vector<int> pool;      // logical features
+  for (int lf = 0; lf < ds_->num_logical_features(); ++lf)
+    if (lp_.feature_mask == nullptr || tree_mask_host_[ds_->logical_first_col[lf]]) pool.push_back(lf);
+  node_pool_size_ = static_cast<int>(pool.size());
+  node_sample_cnt_ = std::max(static_cast<int>(node_pool_size_ * cfg_.feature_fraction_bynode + 0.5), std::min(2, node_pool_size_));
+  node_rand_saved_ = feature_rand_;
+  const int draws = 1 + 2 * (cfg_.num_leaves - 1);
+  std::vector<unsigned char> masks(static_cast<size_t>(draws) * F_, 0);
+  for (int d = 0; d < draws; ++d)
+    for (int i : feature_rand_.Sample(node_pool_size_, node_sample_cnt_)) {
+      const int lf = pool[i];
+      for (int c = 0; c < ds_->logical_num_cols[lf]; ++c) masks[static_cast<size_t>(d) * F_ + ds_->logical_first_col[lf] + c] = 1;
+    }
+  LGB_CUDA(cudaMemcpyAsync(d_node_mask_.p, masks.data(), masks.size(), cudaMemcpyHostToDevice, stream_));
+  LGB_CUDA(cudaStreamSynchronize(stream_));
 }
 
 void Booster::TrainTree(HostTree* out) {
@@ -939,6 +972,7 @@ void Booster::TrainTree(HostTree* out) {
     LGB_CUDA(cudaStreamSynchronize(stream_));
   }
   if (lp_.feature_mask != nullptr) SampleFeaturesForTree();
+  if (lp_.node_mask != nullptr) SampleNodeMasksForTree();
   k_bt_init<<<CeilDiv(L, 256), 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, tree_dev_, L, n,
                                                   static_cast<int>(bagging_ ? bag_cnt_global_ : n_global_));
   LGB_CUDA(cudaMemsetAsync(d_splittable_.p, 1, d_splittable_.bytes(), stream_));
@@ -961,6 +995,14 @@ void Booster::TrainTree(HostTree* out) {
     total += rounds;
     LGB_CUDA(cudaGetLastError());
     if (FetchTree(out)) {
+      if (lp_.node_mask != nullptr) {
+        // upstream never searches the children of the split that fills the tree; here they were searched before that split was
+        // committed: their two samples do not count
+        const bool full = out->num_leaves >= L;
+        const int used = last_node_draws_ - ((full && last_searched_) ? 2 : 0);
+        feature_rand_ = node_rand_saved_;
+        for (int d = 0; d < used; ++d) feature_rand_.Sample(node_pool_size_, node_sample_cnt_);
+      }
       if (renew) { RenewTreeOutput(out); ProfBegin("score_update"); UpdateScores(); ProfEnd(); }
       break;
     }
@@ -1096,6 +1138,7 @@ bool Booster::FetchTree(HostTree* t) {
   CheckAbort(hc);
   if (!hc.done) return false;
   last_rounds_ = hc.rounds;
+  last_node_draws_ = hc.node_draws; last_searched_ = hc.last_searched;
   part_rows_total_ += hc.part_rows;
   rounds_total_ += hc.rounds; expansions_total_ += (hc.num_nodes - 1) / 2; splits_total_ += hc.num_leaves - 1;
   last_rows_visited_ += hc.hist_rows;

@@ -114,6 +114,9 @@ struct LearnerParams {
   // upstream's USE_MC code path — gains taken at clamped outputs — is on for EVERY feature as soon as one column is constrained)
   const signed char* monotone;
   double monotone_penalty;
+  // feature_fraction_bynode < 1: [1 + 2 (L - 1)][F] column samples of this tree in the order the searched leaves use them
+  // (nullptr otherwise); leaves are then expanded one per round, so that order is upstream's
+  const unsigned char* node_mask;
 };
 
 class Booster {
@@ -283,6 +286,11 @@ class Booster {
   DevBuf<unsigned char> d_splittable_;   // [num_leaves][F]
   DevBuf<unsigned char> d_feature_mask_; // [F] this tree's column sample (feature_fraction < 1 only)
   DevBuf<signed char> d_monotone_;       // [F] monotone direction per column (only with monotone_constraints)
+  DevBuf<unsigned char> d_node_mask_;    // feature_fraction_bynode: this tree's by-node column samples
+  HostRandom node_rand_saved_{2};        // the column sampler's stream before this tree's by-node samples were drawn
+  int node_pool_size_ = 0, node_sample_cnt_ = 0, last_node_draws_ = 0, last_searched_ = 0;
+  void SampleNodeMasksForTree();
+  std::vector<unsigned char> tree_mask_host_;      // this tree's by-tree column sample (host copy)
   HostRandom feature_rand_{2};           // ColSampler's stream, seeded with feature_fraction_seed
   void SampleFeaturesForTree();
   bool TrainOneIter(const float* grad, const float* hess);

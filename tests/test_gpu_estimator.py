@@ -104,7 +104,7 @@ def test_unsupported_options_fail_loudly(native):
     X, y = S.higgs_shape(2000)
     df = LocalDataFrame.from_arrays(X, y)
     from synapseml_b200.lightgbm.native import LightGBMNativeError
-    for kw in (dict(boostingType="plain"), dict(objective="cross_entropy"), dict(maxBin=100000), dict(passThroughArgs="feature_fraction_bynode=0.5"),
+    for kw in (dict(boostingType="plain"), dict(objective="cross_entropy"), dict(maxBin=100000), dict(passThroughArgs="feature_fraction_bynode=1.5"),
                dict(passThroughArgs="monotone_constraints=1,0,0")):
         with pytest.raises((LightGBMNativeError, NotImplementedError)):
             LightGBMClassifier(numIterations=1, **kw).fit(df)
@@ -173,7 +173,7 @@ def test_dart_seed_batch_and_prediction_params(native):
                               featureFractionSeed=5, featureFraction=0.8, leafPredictionCol="leaves", featuresShapCol="shap", **kw)
     model = dart.fit(df)
     text = model.getNativeModel()
-    for frag in ("[drop_rate: 0.4]", "[max_drop: 3]", "[skip_drop: 0.1]", "[uniform_drop: True]", "[xgboost_dart_mode: True]", "[drop_seed: 9]",
+    for frag in ("[drop_rate: 0.4]", "[max_drop: 3]", "[skip_drop: 0.1]", "[uniform_drop: true]", "[xgboost_dart_mode: true]", "[drop_seed: 9]",
                  "[feature_fraction_seed: 5]"):
         assert frag in text, frag
     out = model.transform(X[:300])

@@ -21,13 +21,21 @@ CASES = {
     "both_l2": "objective=regression num_leaves=31 max_bin=63 bagging_fraction=0.8 bagging_freq=2 feature_fraction=0.7",
     # more than 32 features: the split search's own last-unit reduction instead of the replay kernel's
     "both_l2_wide": "objective=regression num_leaves=31 max_bin=63 bagging_fraction=0.8 bagging_freq=1 feature_fraction=0.5",
+    # featureFractionByNode (LightGBMParams.scala; ColSampler::GetByNode): a sample per searched leaf, from the tree's own sample
+    # when there is one; trees that fill up, trees that stop early (the number of samples a tree uses decides where the next
+    # tree's stream starts), children that are never searched (max_depth)
+    "bynode": "objective=binary num_leaves=31 max_bin=63 feature_fraction_bynode=0.5",
+    "bynode_and_bytree": "objective=binary num_leaves=15 max_bin=63 feature_fraction=0.7 feature_fraction_bynode=0.6 feature_fraction_seed=5",
+    "bynode_early_stop": "objective=binary num_leaves=63 max_bin=63 feature_fraction_bynode=0.4 min_gain_to_split=40 min_data_in_leaf=200",
+    "bynode_max_depth": "objective=binary num_leaves=31 max_depth=3 max_bin=63 feature_fraction_bynode=0.5 bagging_fraction=0.8 bagging_freq=1",
+    "bynode_l2_wide": "objective=regression num_leaves=31 max_bin=63 feature_fraction_bynode=0.3",
 }
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_quantized_models_with_sampling_are_byte_identical(native, oracle, case):
     params = CASES[case] + QUANT
-    if case.startswith("both_l2"):
+    if case.startswith("both_l2") or case == "bynode_l2_wide":
         X, y = S.dense100(40000, f=48 if case.endswith("wide") else 20)
     else:
         X, y = S.higgs_shape(50000 + 317)         # a ragged last 1024-row bagging block
@@ -35,6 +43,9 @@ def test_quantized_models_with_sampling_are_byte_identical(native, oracle, case)
     ms, mo = nb.model(), ob.save_model_to_string()
     assert strip_parameters(ms) == strip_parameters(mo)
     assert np.array_equal(nb.scores(), ob.scores())          # rows outside the bag are scored through the tree as well
+    if case == "bynode_early_stop":
+        sizes = [t.num_leaves for t in TextModel(ms).trees]
+        assert min(sizes) < 63 and len(set(sizes)) > 1                   # trees that stopped before they were full
     if "feature_fraction" in case:
         used = [set(t.split_feature[:t.num_leaves - 1].tolist()) for t in TextModel(ms).trees]
         assert len(set.union(*used)) > max(len(u) for u in used)      # the trees drew different column samples
@@ -76,7 +87,7 @@ def test_unimplemented_sampling_modes_are_refused(native):
     X, y = S.higgs_shape(5000)
     base = "objective=binary num_leaves=7 max_bin=63 verbosity=-1 "
     nd = NativeDataset(X, y, base)
-    for extra in ("feature_fraction_bynode=0.5", "bagging_freq=1 pos_bagging_fraction=1.5", "monotone_constraints=1,0,-1 monotone_constraints_method=advanced",
+    for extra in ("feature_fraction_bynode=1.5", "bagging_freq=1 pos_bagging_fraction=1.5", "monotone_constraints=1,0,-1 monotone_constraints_method=advanced",
                   "extra_trees=true", "feature_fraction=0"):
         with pytest.raises(Exception):
             NativeBooster(nd, base + extra)
