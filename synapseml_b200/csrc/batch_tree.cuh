@@ -1260,7 +1260,7 @@ __device__ __forceinline__ void SelectBody(NodeDev* nodes, int* avail, BatchCtrl
       it.mono = bs.monotone_type; it.pad2_ = 0; it.cmin = par.cmin; it.cmax = par.cmax;
       it.left_output = bs.left_output; it.right_output = bs.right_output;
       #pragma unroll
-      for (int w = 0; w < 8; ++w) it.cat_bits[w] = bs.cat_bits[w];
+      for (int w = 0; w < 8; ++w) it.cat_bits[w] = bs.is_cat ? bs.cat_bits[w] : 0u;      // (read only for a categorical split)
       it.src_begin = par.begin; it.src_count = par.count; it.src_buf = par.buf;
       it.parent_slot = par.hist_slot; it.fresh_slot = num_slots + pos;
       it.child_depth = par.depth + 1;

@@ -18,7 +18,7 @@ namespace lgb {
 namespace {
 constexpr int kNumSms = 148;
 enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
-       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15, kEvGammaDeviance = 16 };   // (Booster has its own kL2: distinct names)
+       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15, kEvGammaDeviance = 16, kEvMap = 17 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -64,8 +64,14 @@ void Booster::InitMetrics() {
       std::sort(at.begin(), at.end());
       LGB_CHECK(static_cast<int>(at.size()) <= kMaxEvalAt && at.front() > 0, "eval_at: between 1 and %d positive positions are supported", kMaxEvalAt);
       for (int k : at) metrics_.push_back({kEvNdcg, "ndcg@" + std::to_string(k)});
+    } else if (m == "map" || m == "mean_average_precision") {
+      std::vector<int> at = cfg_.eval_at;
+      if (at.empty()) at = {1, 2, 3, 4, 5};
+      std::sort(at.begin(), at.end());
+      LGB_CHECK(static_cast<int>(at.size()) <= kMaxEvalAt && at.front() > 0, "eval_at: between 1 and %d positive positions are supported", kMaxEvalAt);
+      for (int k : at) metrics_.push_back({kEvMap, "map@" + std::to_string(k)});
     } else {
-      LGB_CHECK(false, "metric=%s is not supported by this library (binary_logloss, binary_error, auc, l2, rmse, ndcg)", m.c_str());
+      LGB_CHECK(false, "metric=%s is not supported by this library (binary_logloss, binary_error, auc, l2, rmse, ndcg, map, ...)", m.c_str());
     }
   }
   metrics_ready_ = true;
@@ -164,7 +170,7 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
   d_mpart_.Reserve(kMetricBlocks);
   d_mout_.Reserve(kMaxEvalAt + 2);
   double h[kMaxEvalAt + 2];
-  bool ndcg_done = false;
+  bool ndcg_done = false, map_done = false;
   for (const MetricSpec& m : metrics_) {
     if (m.kind == kEvMultiLogloss || m.kind == kEvMultiError) {
       LGB_CHECK(obj_ == kMulticlass || obj_ == kMulticlassOva, "metric=%s needs objective=multiclass / multiclassova", m.name.c_str());
@@ -177,7 +183,7 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
       continue;
     }
     LGB_CHECK(obj_ != kMulticlass && obj_ != kMulticlassOva, "metric=%s is not defined for multiclass objectives (multi_logloss, multi_error)", m.name.c_str());
-    if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || m.kind >= kEvHuber) {
+    if (m.kind == kEvLogloss || m.kind == kEvError || m.kind == kEvL2 || m.kind == kEvRmse || (m.kind >= kEvHuber && m.kind != kEvMap)) {
       const int kind = m.kind == kEvLogloss ? kMetricBinaryLogloss : m.kind == kEvError ? kMetricBinaryError
                        : m.kind >= kEvL1 ? kMetricL1 + (m.kind - kEvL1) : m.kind >= kEvHuber ? kMetricHuber + (m.kind - kEvHuber) : kMetricL2;
       const double p0 = (m.kind == kEvHuber || m.kind == kEvQuantile) ? cfg_.alpha : m.kind == kEvFair ? cfg_.fair_c : cfg_.tweedie_variance_power;
@@ -235,6 +241,28 @@ void Booster::Eval(int data_idx, std::vector<double>* out) {
       LGB_CUDA(cudaStreamSynchronize(stream_));
       for (int j = 0; j < a.K; ++j) out->push_back(h[j] / h[a.K]);
       ndcg_done = true;
+    } else if (m.kind == kEvMap) {
+      if (map_done) continue;      // all positions come out of one pass
+      PrepareNdcg(vs, ds);         // (query boundaries checked, query weights)
+      NdcgArgs a;
+      a.K = 0;
+      for (auto& mm : metrics_) if (mm.kind == kEvMap) a.eval_at[a.K++] = atoi(mm.name.c_str() + 4);
+      const int nq = static_cast<int>(ds->query_boundaries.size()) - 1;
+      int max_cnt = 1;
+      for (int q = 0; q < nq; ++q) max_cnt = std::max(max_cnt, ds->query_boundaries[q + 1] - ds->query_boundaries[q]);
+      a.score = score; a.label = ds->d_label.p; a.qb = ds->d_query_boundaries.p; a.label_gain = nullptr; a.num_gain = 0; a.max_cnt = max_cnt;
+      d_ndcg_.Reserve(static_cast<size_t>(nq) * a.K);
+      a.dcg = d_ndcg_.p;
+      const size_t smem = (sizeof(double) + sizeof(int)) * max_cnt;
+      LGB_CHECK(smem <= 200 * 1024, "map: a query with %d documents does not fit the kernel's shared memory", max_cnt);
+      static size_t smem_set = 0;
+      if (smem > smem_set) { LGB_CUDA(cudaFuncSetAttribute(k_map, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); smem_set = smem; }
+      k_map<<<nq, kMetricThreads, smem, stream_>>>(a);
+      k_ndcg_final<<<1, kMetricThreads, 0, stream_>>>(d_ndcg_.p, nullptr, vs->qweight.p, nq, a.K, d_mout_.p);
+      LGB_CUDA(cudaMemcpyAsync(h, d_mout_.p, sizeof(double) * (a.K + 1), cudaMemcpyDeviceToHost, stream_));
+      LGB_CUDA(cudaStreamSynchronize(stream_));
+      for (int j = 0; j < a.K; ++j) out->push_back(h[j] / h[a.K]);
+      map_done = true;
     }
   }
   LGB_CUDA(cudaGetLastError());

@@ -218,7 +218,60 @@ __global__ void __launch_bounds__(kMetricThreads) k_ndcg(NdcgArgs a) {
     if (threadIdx.x == 0) a.dcg[static_cast<size_t>(q) * a.K + j] = t;
   }
 }
+// ---- MAP@k (upstream map_metric.hpp, MapMetric::CalMapAtK).  One CTA per query: documents ranked as by std::stable_sort on falling
+// score; every relevant document (label > 0.5) at rank r contributes (relevant documents up to and including r) / (r + 1) to every
+// position k > r; the sum is divided by min(relevant documents, k), and a query without relevant documents scores 1.
+// out[q * K + j] = AP@eval_at[j].  (NdcgArgs: label_gain / num_gain unused.)
+__global__ void __launch_bounds__(kMetricThreads) k_map(NdcgArgs a) {
+  extern __shared__ __align__(16) unsigned char nd_smem[];
+  double* s_score = reinterpret_cast<double*>(nd_smem);
+  int* s_rank = reinterpret_cast<int*>(s_score + a.max_cnt);      // -1 for an irrelevant document
+  __shared__ double s_w[8];
+  const int q = blockIdx.x;
+  const int start = a.qb[q], cnt = a.qb[q + 1] - start;
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) s_score[d] = a.score[start + d];
+  __syncthreads();
+  double npos_part = 0.0;
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+    const bool rel = a.label[start + d] > 0.5f;
+    int rank = -1;
+    if (rel) {
+      const double sd = s_score[d];
+      rank = 0;
+      for (int e = 0; e < cnt; ++e) {
+        const double se = s_score[e];
+        rank += (se > sd) || (se == sd && e < d);
+      }
+      npos_part += 1.0;
+    }
+    s_rank[d] = rank;
+  }
+  __syncthreads();
+  const double npos = BlockSumD(npos_part, s_w);
+  double part[kMaxEvalAt];
+  #pragma unroll
+  for (int j = 0; j < kMaxEvalAt; ++j) part[j] = 0.0;
+  for (int d = threadIdx.x; d < cnt; d += blockDim.x) {
+    const int r = s_rank[d];
+    if (r < 0) continue;
+    int hits = 0;
+    for (int e = 0; e < cnt; ++e) { const int re = s_rank[e]; hits += (re >= 0 && re <= r); }
+    const double term = static_cast<double>(hits) / (r + 1.0f);
+    #pragma unroll
+    for (int j = 0; j < kMaxEvalAt; ++j)
+      if (j < a.K && r < min(a.eval_at[j], cnt)) part[j] += term;
+  }
+  for (int j = 0; j < a.K; ++j) {
+    const double t = BlockSumD(part[j], s_w);
+    if (threadIdx.x == 0) {
+      const double cur_k = static_cast<double>(min(a.eval_at[j], cnt));
+      a.dcg[static_cast<size_t>(q) * a.K + j] = npos > 0.0 ? t / fmin(npos, cur_k) : 1.0;
+    }
+  }
+}
+
 // out[j] = sum_q w_q * (max_dcg > 0 ? dcg / max_dcg : 1), out[K] = sum_q w_q; one CTA, fixed order
+// (inv_max_dcg == nullptr: the per-query values are final already — MAP)
 __global__ void __launch_bounds__(kMetricThreads) k_ndcg_final(const double* __restrict__ dcg, const double* __restrict__ inv_max_dcg,
                                                                 const double* __restrict__ qweight, int nq, int K, double* __restrict__ out) {
   __shared__ double s_w[8];
@@ -227,6 +280,7 @@ __global__ void __launch_bounds__(kMetricThreads) k_ndcg_final(const double* __r
     for (int q = threadIdx.x; q < nq; q += blockDim.x) {
       const double w = qweight ? qweight[q] : 1.0;
       if (j == K) { acc += w; continue; }
+      if (inv_max_dcg == nullptr) { acc += w * dcg[static_cast<size_t>(q) * K + j]; continue; }
       const double inv = inv_max_dcg[static_cast<size_t>(q) * K + j];
       acc += w * (inv > 0.0 ? dcg[static_cast<size_t>(q) * K + j] * inv : 1.0);
     }

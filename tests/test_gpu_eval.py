@@ -118,6 +118,41 @@ def test_ndcg_at_k(native):
     nb.free(); nd.free()
 
 
+def map_ref(score, label, qb, ks):
+    """MapMetric::CalMapAtK written out: sequential, per query, positions in stable order of falling score."""
+    out = np.zeros(len(ks))
+    for a, b in zip(qb[:-1], qb[1:]):
+        s, rel = score[a:b], label[a:b] > 0.5
+        order = np.argsort(-s, kind="stable")
+        npos = int(rel.sum())
+        hits, sum_ap, left = 0, 0.0, 0
+        for j, k in enumerate(ks):
+            kk = min(k, len(s))
+            for pos in range(left, kk):
+                if rel[order[pos]]:
+                    hits += 1
+                    sum_ap += hits / (pos + 1.0)
+            out[j] += sum_ap / min(npos, kk) if npos > 0 else 1.0
+            left = kk
+    return out / (len(qb) - 1)
+
+
+def test_map_at_k(native):
+    """metric=map (LightGBMParams.scala:596 names it for ranking): mean average precision at eval_at, next to ndcg."""
+    X, y, q = S.mslr_shape(30000)
+    params = "objective=lambdarank num_leaves=15 max_bin=63 eval_at=1,3,10 metric=ndcg,map verbosity=-1"
+    nd = NativeDataset(X, y, params, query=q)
+    nb = NativeBooster(nd, params)
+    assert eval_names(nb.handle) == ["ndcg@1", "ndcg@3", "ndcg@10", "map@1", "map@3", "map@10"]
+    qb = np.concatenate([[0], np.flatnonzero(np.diff(q)) + 1, [len(q)]])
+    for _ in range(3):
+        nb.update()
+        got = get_eval(nb.handle, 0, 6)
+        assert np.allclose(got[:3], ndcg_ref(nb.scores(), y, qb, [1, 3, 10]), rtol=0, atol=1e-12)
+        assert np.allclose(got[3:], map_ref(nb.scores(), y, qb, [1, 3, 10]), rtol=0, atol=1e-12)
+    nb.free(); nd.free()
+
+
 def test_early_stopping_through_the_estimator(native):
     # VerifyLightGBMClassifierStream.scala: validationIndicatorCol + earlyStoppingRound; noisy labels make validation loss turn early
     X, y = S.higgs_shape(30000)
