@@ -36,7 +36,9 @@ def main():
         return A                                          # (column 3 has three values already: one category against the rest)
 
     wide = dict(maxBin=1023)      # features with more than 256 bins: several uint8 columns each, searched as one feature
-    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling), (True, cats), (True, wide))):
+    # monotone constraints and per-leaf column samples: both are decided from sums every rank sees alike
+    shaped = dict(monotoneConstraints=[1, -1] + [0] * 26, monotonePenalty=0.5, passThroughArgs="feature_fraction_bynode=0.6")
+    for case, (quant, extra) in enumerate(((True, {}), (False, {}), (True, sampling), (True, cats), (True, wide), (True, shaped))):
         is_cat = "categoricalSlotIndexes" in extra
         Xc = with_cats(X) if is_cat else X
         kw = dict(maxBin=63)
@@ -56,7 +58,7 @@ def main():
             ours, theirs = strip_parameters(model.model_str), strip_parameters(bst.save_model_to_string())
             if quant:
                 same = ours == theirs
-                kind = " categorical" if is_cat else " wide" if "maxBin" in extra else " sampled" if extra else ""
+                kind = " categorical" if is_cat else " wide" if "maxBin" in extra else " constrained" if "monotoneConstraints" in extra else " sampled" if extra else ""
                 if is_cat:
                     same = same and "num_cat=0" not in ours.split("Tree=1")[0]      # the first tree has categorical splits
                 print("quantized%s dp%d model identical to oracle: %s" % (kind, world, same), flush=True)

@@ -33,6 +33,7 @@ def test_data_parallel_matches_oracle(native, world, exchange):
     assert "quantized sampled dp%d model identical to oracle: True" % world in r.stdout
     assert "quantized categorical dp%d model identical to oracle: True" % world in r.stdout
     assert "quantized wide dp%d model identical to oracle: True" % world in r.stdout
+    assert "quantized constrained dp%d model identical to oracle: True" % world in r.stdout
     expect = {"peer": "all-to-all", "sliced": "feature-sliced", "nccl": "NCCL all-reduce exchange"}[exchange]
     assert expect in r.stderr, r.stderr[-2000:]
     log = os.environ.get("LGB_B200_MULTI_LOG")      # profiles/r02_multi_gpu_parity.log is written this way
