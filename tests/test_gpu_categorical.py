@@ -209,3 +209,23 @@ def test_estimator_params_reach_the_native_side(native):
     bad = LightGBMRegressor(numIterations=2, categoricalSlotNames=["nope"], slotNames=names, samplingMode="fixed")
     with pytest.raises(Exception):
         bad.fit(LocalDataFrame.from_arrays(X, z.astype(np.float32)))
+
+
+def test_bulk_and_sparse_ingest_with_categorical_and_wide_features(native):
+    """dataTransferMode=bulk (LGBM_DatasetCreateFromMat, DatasetAggregator.scala:405-421) and sparse partitions (CSR push) build the
+    same bins — and so the same model — as the dense streaming path, with categorical columns and features above 256 bins."""
+    import scipy.sparse as sp
+    from synapseml_b200.lightgbm.estimators import LightGBMClassifier, LocalDataFrame
+    X, y, _ = cat_matrix(30000)
+    X = np.nan_to_num(X)                       # CSR rows cannot carry NaN-as-missing next to implicit zeros
+    X[:, 3] = np.abs(X[:, 3])
+    kw = dict(numIterations=6, numLeaves=15, maxBin=400, categoricalSlotIndexes=[1, 3, 5], useQuantizedGrad=True, stochasticRounding=False,
+              samplingMode="fixed", microBatchSize=4096)
+    stream = LightGBMClassifier(dataTransferMode="streaming", **kw).fit(LocalDataFrame.from_arrays(X, y, num_partitions=2))
+    bulk = LightGBMClassifier(dataTransferMode="bulk", **kw).fit(LocalDataFrame.from_arrays(X, y, num_partitions=2))
+    sparse = LightGBMClassifier(dataTransferMode="streaming", **kw).fit(
+        LocalDataFrame([dict(features=sp.csr_matrix(X[:15000]), label=y[:15000]), dict(features=sp.csr_matrix(X[15000:]), label=y[15000:])]))
+    a = strip_parameters(stream.getNativeModel())
+    assert a == strip_parameters(bulk.getNativeModel()) == strip_parameters(sparse.getNativeModel())
+    tm = TextModel(stream.getNativeModel())
+    assert sum(t.num_cat for t in tm.trees if t.num_leaves > 1) > 0
