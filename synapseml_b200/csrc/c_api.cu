@@ -532,19 +532,57 @@ int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_ty
   *out_len = static_cast<Booster*>(handle)->CalcNumPredict(num_row, predict_type, start_iteration, num_iteration);
   API_END();
 }
+namespace {
+// predict_disable_shape_check=true in the prediction parameter string (LightGBMBooster.scala:526,548 always sends the key): rows with
+// another number of columns than the model was trained on are accepted — columns the model does not know are ignored, columns the
+// rows lack read as 0.0 (what upstream's predictor does with its zero-initialised feature buffer).
+bool ShapeCheckDisabled(const char* parameter) {
+  if (parameter == nullptr) return false;
+  Config c;
+  c.Set(parameter);
+  auto it = c.raw.find("predict_disable_shape_check");
+  if (it == c.raw.end()) return false;
+  const std::string& v = it->second;
+  return v == "true" || v == "True" || v == "1" || v == "+";
+}
+// rows repacked to the model's width (a host-side formatting step), row-major float64
+std::vector<double> RepackRows(const void* data, int data_type, int64_t nrow, int ncol, bool row_major, int want) {
+  std::vector<double> out(static_cast<size_t>(std::max<int64_t>(nrow, 0)) * want, 0.0);
+  const int keep = std::min(ncol, want);
+  for (int64_t i = 0; i < nrow; ++i)
+    for (int j = 0; j < keep; ++j) {
+      const size_t at = row_major ? static_cast<size_t>(i) * ncol + j : static_cast<size_t>(j) * nrow + i;
+      out[static_cast<size_t>(i) * want + j] = data_type == C_API_DTYPE_FLOAT64 ? static_cast<const double*>(data)[at]
+                                                                                 : static_cast<double>(static_cast<const float*>(data)[at]);
+    }
+  return out;
+}
+void PredictRows(Booster* b, const void* data, int data_type, int64_t nrow, int ncol, bool row_major, int predict_type, int start_iteration,
+                 int num_iteration, const char* parameter, int64_t* out_len, double* out_result) {
+  LGB_CHECK(data_type == C_API_DTYPE_FLOAT32 || data_type == C_API_DTYPE_FLOAT64, "Predict: data_type must be C_API_DTYPE_FLOAT32 or FLOAT64");
+  const int want = b->NumTotalFeatures();
+  if (ncol != want && ncol > 0 && ShapeCheckDisabled(parameter)) {
+    const std::vector<double> rows = RepackRows(data, data_type, nrow, ncol, row_major, want);
+    b->PredictForMat(rows.data(), C_API_DTYPE_FLOAT64, nrow, want, true, predict_type, start_iteration, num_iteration, out_result, out_len);
+    return;
+  }
+  b->PredictForMat(data, data_type, nrow, ncol, row_major, predict_type, start_iteration, num_iteration, out_result, out_len);
+}
+}  // namespace
+
 int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
-                              int predict_type, int start_iteration, int num_iteration, const char* /*parameter*/, int64_t* out_len,
+                              int predict_type, int start_iteration, int num_iteration, const char* parameter, int64_t* out_len,
                               double* out_result) {
   API_BEGIN();
-  static_cast<Booster*>(handle)->PredictForMat(data, data_type, nrow, ncol, is_row_major != 0, predict_type, start_iteration,
-                                               num_iteration, out_result, out_len);
+  PredictRows(static_cast<Booster*>(handle), data, data_type, nrow, ncol, is_row_major != 0, predict_type, start_iteration, num_iteration,
+              parameter, out_len, out_result);
   API_END();
 }
 // Sparse rows for scoring (LightGBMBooster.scala:520-538, predictForCSR): the rows are expanded to dense (absent = 0.0, a host-side
 // formatting step) and scored by the same GPU kernel as PredictForMat.
 int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices, const void* data,
                               int data_type, int64_t nindptr, int64_t nelem, int64_t num_col, int predict_type, int start_iteration,
-                              int num_iteration, const char* /*parameter*/, int64_t* out_len, double* out_result) {
+                              int num_iteration, const char* parameter, int64_t* out_len, double* out_result) {
   API_BEGIN();
   LGB_CHECK(indptr_type == C_API_DTYPE_INT32 || indptr_type == C_API_DTYPE_INT64, "PredictForCSR: indptr must be int32 or int64");
   LGB_CHECK(data_type == C_API_DTYPE_FLOAT64 || data_type == C_API_DTYPE_FLOAT32, "PredictForCSR: data must be float32 or float64");
@@ -564,7 +602,7 @@ int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indp
       dense[static_cast<size_t>(i) * ncol + c] =
           data_type == C_API_DTYPE_FLOAT64 ? static_cast<const double*>(data)[j] : static_cast<double>(static_cast<const float*>(data)[j]);
     }
-  b->PredictForMat(dense.data(), C_API_DTYPE_FLOAT64, nrow, ncol, true, predict_type, start_iteration, num_iteration, out_result, out_len);
+  PredictRows(b, dense.data(), C_API_DTYPE_FLOAT64, nrow, ncol, true, predict_type, start_iteration, num_iteration, parameter, out_len, out_result);
   API_END();
 }
 int LGBM_BoosterPredictForCSRSingleRow(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices,
@@ -575,11 +613,11 @@ int LGBM_BoosterPredictForCSRSingleRow(BoosterHandle handle, const void* indptr,
                                    start_iteration, num_iteration, parameter, out_len, out_result);
 }
 int LGBM_BoosterPredictForMatSingleRow(BoosterHandle handle, const void* data, int data_type, int ncol, int is_row_major,
-                                       int predict_type, int start_iteration, int num_iteration, const char* /*parameter*/,
+                                       int predict_type, int start_iteration, int num_iteration, const char* parameter,
                                        int64_t* out_len, double* out_result) {
   API_BEGIN();
-  static_cast<Booster*>(handle)->PredictForMat(data, data_type, 1, ncol, is_row_major != 0, predict_type, start_iteration, num_iteration,
-                                               out_result, out_len);
+  PredictRows(static_cast<Booster*>(handle), data, data_type, 1, ncol, is_row_major != 0, predict_type, start_iteration, num_iteration,
+              parameter, out_len, out_result);
   API_END();
 }
 

@@ -30,8 +30,9 @@ class LightGBMBooster:
     # predict_type constants of the C API (C_API_PREDICT_NORMAL / RAW_SCORE / LEAF_INDEX)
     PREDICT_NORMAL, PREDICT_RAW, PREDICT_LEAF, PREDICT_CONTRIB = 0, 1, 2, 3
 
-    def predict_for_mat(self, features, predict_type=0, start_iteration=0, num_iteration=-1):
-        """Batch scoring on the GPU: one LGBM_BoosterPredictForMat call for all rows."""
+    def predict_for_mat(self, features, predict_type=0, start_iteration=0, num_iteration=-1, disable_shape_check=False):
+        """Batch scoring on the GPU: one LGBM_BoosterPredictForMat call for all rows.  The parameter string is the reference's
+        (LightGBMBooster.scala:526,548): max_bin=255 predict_disable_shape_check=<bool>."""
         lib = lightgbmlib()
         x = np.ascontiguousarray(features, dtype=np.float64)
         if x.ndim == 1:
@@ -44,7 +45,8 @@ class LightGBMBooster:
         out_len = C.c_int64()
         validate(lib.LGBM_BoosterPredictForMat(self.booster_handle, x.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(n), C.c_int32(ncol),
                                                C.c_int(1), C.c_int(predict_type), C.c_int(start_iteration), C.c_int(num_iteration),
-                                               b"", C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
+                                               ("max_bin=255 predict_disable_shape_check=%s" % ("true" if disable_shape_check else "false")).encode(),
+                                               C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
         out = out[:out_len.value]
         return out.reshape(n, -1) if predict_type in (self.PREDICT_LEAF, self.PREDICT_CONTRIB) else out
 

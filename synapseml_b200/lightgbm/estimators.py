@@ -340,6 +340,7 @@ class LightGBMBase:
         model.best_iteration = self.best_iteration
         model.leafPredictionCol, model.featuresShapCol = g["leafPredictionCol"], g["featuresShapCol"]
         model.startIteration = g["startIteration"]
+        model.predictDisableShapeCheck = bool(g["predictDisableShapeCheck"])
         return model
 
     def add_custom_train_params(self, train_params, df, dist):
@@ -363,6 +364,7 @@ class LightGBMModelBase:
         self._booster = None
         # LightGBMPredictionParams: optional output columns of transform, and the first iteration used for prediction
         self.leafPredictionCol, self.featuresShapCol, self.startIteration = "", "", 0
+        self.predictDisableShapeCheck = False
 
     def setLeafPredictionCol(self, v):
         self.leafPredictionCol = v
@@ -385,7 +387,12 @@ class LightGBMModelBase:
         return out
 
     def _predict(self, features, predict_type):
-        return self._native().predict_for_mat(features, predict_type, start_iteration=self.startIteration)
+        return self._native().predict_for_mat(features, predict_type, start_iteration=self.startIteration,
+                                              disable_shape_check=self.predictDisableShapeCheck)
+
+    def setPredictDisableShapeCheck(self, v):
+        self.predictDisableShapeCheck = bool(v)
+        return self
 
     def _native(self):
         if self._booster is None:

@@ -190,3 +190,21 @@ def test_dart_seed_batch_and_prediction_params(native):
     assert roc_auc_score(y, bm.predict_raw(X)) > roc_auc_score(y, LightGBMClassifier(**kw).fit(df).predict_raw(X)) - 0.01
     with pytest.raises(ValueError):
         LightGBMClassifier(objective="multiclass", maxNumClasses=1, **kw).fit(df)
+
+
+def test_predict_disable_shape_check(native):
+    """predictDisableShapeCheck (LightGBMParams.scala:344-349 -> predict_disable_shape_check in the scoring parameter string,
+    LightGBMBooster.scala:526): rows wider or narrower than the training data are refused unless the check is disabled; then extra
+    columns are ignored and missing ones read as 0."""
+    X, y = S.higgs_shape(20000)
+    model = LightGBMClassifier(numIterations=5, numLeaves=15, samplingMode="fixed").fit(LocalDataFrame.from_arrays(X, y))
+    want = model.predict_raw(X[:200])
+    wide = np.concatenate([X[:200], np.ones((200, 3))], axis=1)
+    from synapseml_b200.lightgbm.native import LightGBMNativeError
+    with pytest.raises(LightGBMNativeError):
+        model.predict_raw(wide)
+    model.setPredictDisableShapeCheck(True)
+    assert np.array_equal(model.predict_raw(wide), want)
+    narrow = X[:200, :20]
+    padded = np.concatenate([narrow, np.zeros((200, 8))], axis=1)
+    assert np.array_equal(model.predict_raw(narrow), model.predict_raw(padded))
