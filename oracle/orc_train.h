@@ -656,7 +656,8 @@ class Booster {
 
   // SerialTreeLearner::RenewTreeOutput with the objective's RenewTreeOutput (l1 / quantile / mape): every leaf's output becomes the
   // (weighted) percentile of label - score over the leaf's rows on each machine; machines that hold rows of the leaf are averaged.
-  void RenewTreeOutput(Tree* tree) {
+  // const_pred: a random forest re-fits against label - initial score (RF::TrainOneIter's residual_getter), boosting against label - score
+  void RenewTreeOutput(Tree* tree, const double* const_pred = nullptr) {
     const double a = obj == OBJ_QUANTILE ? cfg.alpha : 0.5;
     const bool af = obj == OBJ_QUANTILE;
     for (int l = 0; l < tree->num_leaves; ++l) {
@@ -670,7 +671,7 @@ class Booster {
         std::vector<label_t> w(n);
         for (data_size_t i = 0; i < n; ++i) {
           const data_size_t r = sh.indices[b + i];
-          res[i] = static_cast<double>(sh.ds->label[r]) - sh.score[r];
+          res[i] = static_cast<double>(sh.ds->label[r]) - (const_pred != nullptr ? *const_pred : sh.score[r]);
           if (obj == OBJ_MAPE) w[i] = label_weight[s][r]; else if (has_weights) w[i] = sh.ds->weight[r];
         }
         double out;
@@ -1599,6 +1600,7 @@ class Booster {
       if (train_this && F > 0) tree = TrainTree();
       bool add = false;
       if (tree->num_leaves > 1) {
+        if (RenewsLeaves()) { const double pred = rf_init_scores[k]; RenewTreeOutput(tree.get(), &pred); }
         if (std::fabs(rf_init_scores[k]) > kEpsilon) tree->AddBias(rf_init_scores[k]);
         add = true;
       } else if (static_cast<int>(models.size()) < K) {

@@ -1403,7 +1403,7 @@ template <int ES>
 __global__ void k_renew_collect(const NodeDev* __restrict__ nodes, const int* __restrict__ avail, const BatchCtrl* __restrict__ ctrl,
                                 const int* __restrict__ off, const int* __restrict__ idx0, const int* __restrict__ idx1,
                                 const float* __restrict__ label, const double* __restrict__ score, const float* __restrict__ weight,
-                                double* __restrict__ res, float* __restrict__ wout) {
+                                double* __restrict__ res, float* __restrict__ wout, int use_const_pred, double const_pred) {
   const int l = blockIdx.x;
   if (!ctrl->done || ctrl->abort || l >= ctrl->num_leaves || ctrl->num_leaves <= 1) return;
   const NodeDev& nd = nodes[avail[l]];
@@ -1411,7 +1411,8 @@ __global__ void k_renew_collect(const NodeDev* __restrict__ nodes, const int* __
   const int o = off[l];
   for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < nd.count; p += gridDim.y * blockDim.x) {
     const int row = idx[static_cast<size_t>(nd.begin + p) * ES];
-    res[o + p] = static_cast<double>(label[row]) - score[row];
+    // (a random forest re-fits against label - initial score: RF::TrainOneIter's residual_getter)
+    res[o + p] = static_cast<double>(label[row]) - (use_const_pred ? const_pred : score[row]);
     if (weight != nullptr) wout[o + p] = weight[row];
   }
 }

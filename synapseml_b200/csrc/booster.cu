@@ -617,8 +617,11 @@ void Booster::ComputeGradients(const double* score_override) {
     a.max_sigmoid_input = max_sigmoid_input_; a.idx_factor = sigmoid_table_idx_factor_;
     a.truncation_level = cfg_.lambdarank_truncation_level; a.norm = cfg_.lambdarank_norm; a.table_size = 1024 * 1024;
     auto smem_for = [](int max_cnt) { return static_cast<size_t>(max_cnt) * (2 * sizeof(double) + 5 * sizeof(float) + sizeof(int)) + 16; };
+    // the attribute is the LIMIT of what a launch may ask for: it must cover the short-query launch too (it asks for short_query_len_
+    // documents even when the longest query is shorter — a limit set from the longest query alone refused that launch)
     static size_t smem_set = 0;
-    if (smem_for(max_query_len_) > smem_set) { smem_set = smem_for(max_query_len_); SetSmem(k_grad_lambdarank, smem_set); }
+    const size_t smem_need = std::max(smem_for(max_query_len_), smem_for(short_query_len_));
+    if (smem_need > smem_set) { smem_set = smem_need; SetSmem(k_grad_lambdarank, smem_set); }
     // long queries first (they are the tail), then the short ones with a small shared-memory footprint (more CTAs per SM)
     if (n_long_queries_ > 0) {
       a.max_cnt = max_query_len_; a.qlist = d_query_order_.p;
@@ -1085,12 +1088,14 @@ void Booster::RenewTreeOutput(HostTree* tree) {
   for (int k = 0; k < 2; ++k) { d_renew_res_[k].Reserve(n_); if (weighted) d_renew_w_[k].Reserve(n_); }
   k_renew_offsets<<<1, 32, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, L, d_renew_off_.p);
   const dim3 cgrid(nl, std::max(1, std::min(64, static_cast<int>(n_ / (1024 * static_cast<int64_t>(nl)) + 1))));
+  const int rf_pred_on = boost_ == kRF ? 1 : 0;
+  const double rf_pred = boost_ == kRF ? rf_init_scores_[cls_] : 0.0;
   if (idx_es_ == 2)
     k_renew_collect<2><<<cgrid, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_renew_off_.p, d_idx_[0].p, d_idx_[1].p, ds_->d_label.p,
-                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p);
+                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p, rf_pred_on, rf_pred);
   else
     k_renew_collect<4><<<cgrid, 256, 0, stream_>>>(d_nodes_, d_avail_.p, d_ctrl_, d_renew_off_.p, d_idx_[0].p, d_idx_[1].p, ds_->d_label.p,
-                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p);
+                                                   d_score_.p + cls_ * n_, w, d_renew_res_[0].p, d_renew_w_[0].p, rf_pred_on, rf_pred);
   size_t tmp = 0;
   const int n = static_cast<int>(n_);
   if (weighted)
