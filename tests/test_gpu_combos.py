@@ -3,10 +3,15 @@ features), missing-value handling, monotone constraints, column / row sampling, 
 iterations in quantized mode on the GPU and by the oracle: the models must be byte-identical.  The single-option tests pin each
 feature; this one pins their interactions (categorical + zero_as_missing, wide features + constraints + sampling, rf / dart / goss on
 categorical data, ...)."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
 from helpers import NativeBooster, NativeDataset, oracle_dataset, strip_parameters
+from synapseml_b200.lightgbm.booster import LightGBMBooster
+from synapseml_b200.lightgbm.model_text import TextModel
+from synapseml_b200.lightgbm.native import lightgbmlib, validate
 
 pytestmark = pytest.mark.gpu
 
@@ -104,5 +109,35 @@ def test_random_option_combinations_are_byte_identical(native, oracle, seed):
         assert np.allclose(a, b, rtol=0, atol=1e-12), params
     else:
         assert np.array_equal(a, b), params
+    # scoring on raw values — unseen / negative / fractional categories, NaNs and zeros included — against an independent traversal
+    # of the model text; leaf indices; feature contributions sum to the raw score; the model string survives a reload
+    ms = nb.model()
+    tm = TextModel(ms)
+    Xp = X[:1500].copy()
+    Xp[:100, 3] = 77; Xp[100:200, 3] = -4; Xp[200:300, 1] = 2.7; Xp[300:400, 0] = np.nan; Xp[400:500, 2] = 0.0; Xp[500:600, 4] = 0.0
+    K = tm.num_tree_per_iteration
+    raw = predict(nb.handle, Xp, 1).reshape(len(Xp), K)
+    assert np.array_equal(raw, tm.predict_raw(Xp).reshape(len(Xp), K)), params
+    leaves = predict(nb.handle, Xp, 2).reshape(len(Xp), -1)
+    assert np.array_equal(leaves.astype(np.int64), np.stack([t.predict_leaf(Xp) for t in tm.trees], axis=1)), params
+    contrib = predict(nb.handle, Xp[:200], 3).reshape(200, K, X.shape[1] + 1)
+    assert np.allclose(contrib.sum(axis=2), raw[:200], rtol=0, atol=1e-9), params
+    lb = LightGBMBooster(model_str=ms)
+    assert lb.save_to_string() == ms
+    assert np.array_equal(lb.predict_for_mat(Xp, LightGBMBooster.PREDICT_RAW).reshape(len(Xp), K), raw), params
+    lb.free_native_memory()
     nb.free()
     nd.free()
+
+
+def predict(handle, X, predict_type):
+    lib = lightgbmlib()
+    n, f = X.shape
+    x = np.ascontiguousarray(X, dtype=np.float64)
+    need = C.c_int64()
+    validate(lib.LGBM_BoosterCalcNumPredict(handle, n, predict_type, 0, -1, C.byref(need)))
+    out = np.full(max(need.value, 1), np.nan)
+    got = C.c_int64()
+    validate(lib.LGBM_BoosterPredictForMat(handle, x.ctypes.data_as(C.c_void_p), 1, n, f, 1, predict_type, 0, -1, b"", C.byref(got),
+                                           out.ctypes.data_as(C.POINTER(C.c_double))))
+    return out[:got.value]
