@@ -1477,6 +1477,19 @@ void Booster::CopyScores(double* out) const {
   LGB_CUDA(cudaMemcpy(out, d_score_.p, sizeof(double) * n_ * K_, cudaMemcpyDeviceToHost));      // class-major [K][n]
 }
 
+int64_t Booster::NumValidRows(int i) const {
+  LGB_CHECK(i >= 0 && i < static_cast<int>(valids_.size()), "validation data %d does not exist", i + 1);
+  return valids_[i].ds->num_data;
+}
+
+int64_t Booster::CopyValidScores(int i, double* out) const {
+  const int64_t n = NumValidRows(i);
+  LGB_CUDA(cudaSetDevice(device_));
+  Sync();
+  LGB_CUDA(cudaMemcpy(out, valids_[i].score.p, sizeof(double) * n * K_, cudaMemcpyDeviceToHost));
+  return n;
+}
+
 void Booster::CopyGradients(float* g, float* h) const {
   LGB_CUDA(cudaSetDevice(device_));
   Sync();

@@ -136,6 +136,9 @@ class Booster {
   // LGBM_BoosterMerge (upstream GBDT::MergeFrom): the other booster's trees go in front of this one's; scores are not touched
   void MergeFrom(const Booster& other);
   void CopyScores(double* out) const;
+  // scores of validation set i (LGBM_BoosterGetPredict with data_idx = i + 1), class-major; returns its row count
+  int64_t CopyValidScores(int i, double* out) const;
+  int64_t NumValidRows(int i) const;
   void CopyGradients(float* g, float* h) const;
   void CopyQuantGradients(int8_t* g, int8_t* h, double* scales) const;
   // GPU prediction on raw feature values (predict_kernel.cuh).  data_type: 0 float32, 1 float64; predict_type: 0 normal, 1 raw,

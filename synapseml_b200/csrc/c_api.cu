@@ -332,11 +332,16 @@ int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out) { API_BEGIN(
 
 int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result) {
   API_BEGIN();
-  LGB_CHECK(data_idx == 0, "LGBM_BoosterGetPredict: only the training data (data_idx 0) is available");
   auto b = static_cast<Booster*>(handle);
   LGB_CHECK(!b->predict_only(), "LGBM_BoosterGetPredict: a booster loaded from a model string has no training data");
-  *out_len = b->train()->num_data * b->NumClasses();      // class-major [num_class][num_data], as upstream
-  b->CopyScores(out_result);
+  if (data_idx > 0) {      // validation data data_idx - 1, in the order of LGBM_BoosterAddValidData
+    *out_len = b->NumValidRows(data_idx - 1) * b->NumClasses();
+    b->CopyValidScores(data_idx - 1, out_result);
+  } else {
+    LGB_CHECK(data_idx == 0, "LGBM_BoosterGetPredict: negative data_idx");
+    *out_len = b->train()->num_data * b->NumClasses();      // class-major [num_class][num_data], as upstream
+    b->CopyScores(out_result);
+  }
   API_END();
 }
 

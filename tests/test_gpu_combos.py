@@ -99,6 +99,18 @@ def test_random_option_combinations_are_byte_identical(native, oracle, seed):
         query = np.repeat(np.arange(len(sizes)), sizes)[:len(y)].astype(np.int32)
     nd = NativeDataset(X, y, params, weight=w, query=query, micro_batches=[4096, 100])
     nb = NativeBooster(nd, params)
+    # a validation set (other rows of the same distribution, built on the training data's bin mappers): its scores are advanced by
+    # the training loop through the tree walk over bins and must equal a fresh prediction on the raw values
+    Xv, zv, rngv = combo_data(3000, 10_000 + seed)
+    Xv[:200, 3] = 55
+    if "zero_as_missing" not in params:
+        # (under zero_as_missing a value below everything the sample held lands in the zero bin, i.e. counts as missing over bins but
+        # not over values — upstream's own inconsistency between training-time validation scores and prediction; not probed here)
+        Xv[200:300, 1] = -1
+    vq = None if query is None else np.repeat(np.arange(100), 30).astype(np.int32)
+    vd = NativeDataset(Xv, labels_for(objective, zv, rngv), params, query=vq, weight=None if w is None else np.ones(len(Xv), dtype=np.float32),
+                       serialized=nd.serialized)
+    validate(nb.lib.LGBM_BoosterAddValidData(nb.handle, vd.handle))
     _, dss, _ = oracle_dataset(oracle, X, y, params, weight=w, query=query)
     ob = oracle.Booster(dss, params)
     for _ in range(6):
@@ -122,11 +134,18 @@ def test_random_option_combinations_are_byte_identical(native, oracle, seed):
     assert np.array_equal(leaves.astype(np.int64), np.stack([t.predict_leaf(Xp) for t in tm.trees], axis=1)), params
     contrib = predict(nb.handle, Xp[:200], 3).reshape(200, K, X.shape[1] + 1)
     assert np.allclose(contrib.sum(axis=2), raw[:200], rtol=0, atol=1e-9), params
+    vs = np.zeros(len(Xv) * K)
+    vn = C.c_int64()
+    validate(nb.lib.LGBM_BoosterGetPredict(nb.handle, 1, C.byref(vn), vs.ctypes.data_as(C.POINTER(C.c_double))))
+    assert vn.value == len(Xv) * K
+    fresh = predict(nb.handle, Xv, 1).reshape(len(Xv), K)
+    assert np.allclose(vs.reshape(K, len(Xv)).T, fresh, rtol=0, atol=1e-10), params      # (RF / DART rescale running sums: not bit-equal)
     lb = LightGBMBooster(model_str=ms)
     assert lb.save_to_string() == ms
     assert np.array_equal(lb.predict_for_mat(Xp, LightGBMBooster.PREDICT_RAW).reshape(len(Xp), K), raw), params
     lb.free_native_memory()
     nb.free()
+    vd.free()
     nd.free()
 
 
