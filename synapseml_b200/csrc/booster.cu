@@ -414,7 +414,12 @@ void Booster::Sync() const { LGB_CUDA(cudaStreamSynchronize(stream_)); }
 void Booster::ResetParameter(const char* params) {
   Config c;
   c.Set(params ? params : "");
-  if (c.raw.count("learning_rate")) { cfg_.learning_rate = c.learning_rate; lp_.learning_rate = c.learning_rate; cfg_.raw["learning_rate"] = c.raw["learning_rate"]; }
+  if (c.raw.count("learning_rate")) {
+    LGB_CHECK(c.learning_rate > 0.0, "learning_rate must be positive");
+    cfg_.learning_rate = c.learning_rate; lp_.learning_rate = c.learning_rate; cfg_.raw["learning_rate"] = c.raw["learning_rate"];
+    // GBDT::ResetConfig: the shrinkage of the trees still to come (a forest keeps 1, DART recomputes its own every iteration)
+    if (boost_ != kRF) shrinkage_rate_ = cfg_.learning_rate;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------- objectives

@@ -265,3 +265,32 @@ def test_zero_as_missing(native, oracle, mode, monkeypatch):
     assert strip_parameters(nw.model()) == strip_parameters(ms)
     nw.free()
     nd.free()
+
+
+def test_reset_parameter_changes_the_learning_rate_of_later_trees(native):
+    """LGBM_BoosterResetParameter("learning_rate=...") is how the reference's delegate changes the learning rate between iterations
+    (TrainUtils.scala:98-135 -> LightGBMBooster.resetParameter): the trees that follow are shrunk by the new rate."""
+    import ctypes as C
+    from synapseml_b200.lightgbm.native import validate
+    X, y = S.higgs_shape(30000)
+    params = "objective=binary num_leaves=15 max_bin=63 learning_rate=0.1 use_quantized_grad=true stochastic_rounding=false verbosity=-1"
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    for _ in range(3):
+        nb.update()
+    validate(nb.lib.LGBM_BoosterResetParameter(nb.handle, b"learning_rate=0.5"))
+    for _ in range(2):
+        nb.update()
+    text = nb.model()
+    shr = [float(l.split("=")[1]) for l in text.split("\n") if l.startswith("shrinkage=")]
+    assert shr == [1.0, 0.1, 0.1, 0.5, 0.5]               # (the first tree carries the initial score: AddBias resets it to 1)
+    m = TextModel(text)
+    assert np.allclose(m.predict_raw(X), nb.scores(), rtol=0, atol=1e-12)
+    assert np.abs(m.trees[3].leaf_value).max() > 2 * np.abs(m.trees[2].leaf_value).max()
+    # a model trained at 0.5 throughout differs, one trained at 0.1 throughout agrees on the first three trees
+    nb2 = NativeBooster(nd, params)
+    for _ in range(3):
+        nb2.update()
+    m2 = TextModel(nb2.model())
+    assert m2.structure() == m.structure()[:3] and all(np.array_equal(a.leaf_value, b.leaf_value) for a, b in zip(m2.trees, m.trees))
+    nb2.free(); nb.free(); nd.free()
