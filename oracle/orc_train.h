@@ -473,7 +473,7 @@ class Booster {
   // objective state
   enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA } obj = OBJ_L2;
   std::vector<int> mono_inner;             // monotone direction per inner feature (empty: no constraints at all)
-  bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA; }
+  bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA || (obj == OBJ_CUSTOM && K > 1); }
   std::vector<double> ova_label_weights, ova_suml;      // multiclassova: per class [neg, pos] label weights and the weighted positives
   double ova_sumw = 0.0;
   bool RenewsLeaves() const { return obj == OBJ_L1 || obj == OBJ_QUANTILE || obj == OBJ_MAPE; }      // IsRenewTreeOutput
@@ -883,6 +883,16 @@ class Booster {
       }
     } else if (cfg.objective == "custom" || cfg.objective == "none") {
       obj = OBJ_CUSTOM;      // no objective function: gradients come from the caller (TrainOneIter(grad, hess))
+      K = std::max(1, cfg.num_class);      // num_tree_per_iteration = num_class also without an objective (GBDT::Init)
+      if (K > 1) {
+        class_need_train.assign(K, 1);
+        for (auto& sh : shards) {
+          const size_t n = sh.score.size();
+          sh.score_k.assign(K, std::vector<double>(n, 0.0));
+          sh.grad_k.assign(K, std::vector<score_t>(n, 0.0f));
+          sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
+        }
+      }
     } else if (cfg.objective == "lambdarank") {
       obj = OBJ_LAMBDARANK;
       label_gain = cfg.label_gain;
@@ -1476,7 +1486,7 @@ class Booster {
     const bool custom = custom_grad != nullptr;
     const bool multi = IsMulti();
     if (obj == OBJ_CUSTOM && !custom) throw std::runtime_error("oracle: objective=custom needs caller-supplied gradients");
-    if (multi && custom) throw std::runtime_error("oracle: caller-supplied gradients with multiclass are not restated");
+    if (multi && custom && obj != OBJ_CUSTOM) throw std::runtime_error("oracle: caller-supplied gradients next to a multiclass objective are not restated");
     // multiclass: class k's scores / gradients take the place of the single-class arrays while its tree is handled
     auto enter_class = [&](int k, bool with_grad) {
       cur_class = k;
@@ -1512,9 +1522,16 @@ class Booster {
     if (boost == BOOST_DART) DroppingTrees();      // DART::GetTrainingScore: before the gradients are taken
     if (custom) {
       size_t off = 0;
-      for (auto& sh : shards) {
-        for (size_t i = 0; i < sh.grad.size(); ++i) { sh.grad[i] = custom_grad[off + i]; sh.hess[i] = custom_hess[off + i]; }
-        off += sh.grad.size();
+      for (auto& sh : shards) {      // per machine: one value per row, class after class ([num_class][num_data], as upstream)
+        const size_t n = sh.grad.size();
+        if (multi) {
+          for (int k = 0; k < K; ++k)
+            for (size_t i = 0; i < n; ++i) { sh.grad_k[k][i] = custom_grad[off + k * n + i]; sh.hess_k[k][i] = custom_hess[off + k * n + i]; }
+          off += n * K;
+        } else {
+          for (size_t i = 0; i < n; ++i) { sh.grad[i] = custom_grad[off + i]; sh.hess[i] = custom_hess[off + i]; }
+          off += n;
+        }
       }
     } else {
       GetGradients();      // Boosting(): all classes at once

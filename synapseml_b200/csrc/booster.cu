@@ -572,6 +572,10 @@ void Booster::InitObjective() {
     }
   } else if (cfg_.objective == "custom" || cfg_.objective == "none" || cfg_.objective == "null" || cfg_.objective == "na") {
     obj_ = kCustom;      // no objective function: LGBM_BoosterUpdateOneIterCustom supplies the gradients, scores stay raw
+    K_ = std::max(1, cfg_.num_class);      // num_tree_per_iteration = num_class also without an objective (GBDT::Init): the caller's arrays
+                                           // then hold one value per row and class, class after class (FObjTrait with a multiclass label)
+    LGB_CHECK(K_ <= kMaxClasses, "num_class=%d is above %d", K_, kMaxClasses);
+    if (K_ > 1) class_need_train_.assign(K_, 1);
   } else {
     throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, multiclassova, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
   }
@@ -1283,7 +1287,7 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   LGB_CUDA(cudaSetDevice(device_));
   const double kEps = 1e-15f;
   const bool custom = custom_grad != nullptr;
-  LGB_CHECK(!(custom && K_ > 1), "LGBM_BoosterUpdateOneIterCustom with multiclass is not supported by this library yet");
+  LGB_CHECK(!(custom && K_ > 1 && obj_ != kCustom), "LGBM_BoosterUpdateOneIterCustom next to a multiclass objective is not supported (use objective=custom)");
   // ObtainAutomaticInitialScore (upstream src/boosting/gbdt.cpp): the objective's BoostFromScore over the labels of all machines,
   // then the mean over machines of what are identical values
   auto automatic_init_score = [&]() -> double {
@@ -1369,8 +1373,8 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   if (any_train && F_ > 0) {
     if (fused) grad_cur_ ^= 1;
     else if (custom) {       // pageable sources are staged before the calls return
-      LGB_CUDA(cudaMemcpyAsync(d_grad_[grad_cur_].p, custom_grad, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
-      LGB_CUDA(cudaMemcpyAsync(d_hess_[grad_cur_].p, custom_hess, sizeof(float) * n_, cudaMemcpyHostToDevice, stream_));
+      LGB_CUDA(cudaMemcpyAsync(d_grad_[grad_cur_].p, custom_grad, sizeof(float) * n_ * K_, cudaMemcpyHostToDevice, stream_));
+      LGB_CUDA(cudaMemcpyAsync(d_hess_[grad_cur_].p, custom_hess, sizeof(float) * n_ * K_, cudaMemcpyHostToDevice, stream_));
     } else if (boost_ != kRF) { ProfBegin("gradients"); ComputeGradients(); ProfEnd(); }
     grad_ready_ = false;
     Bagging();
@@ -1455,7 +1459,7 @@ ModelHeader Booster::MakeHeader() const {
     h.num_class = K_; h.num_tree_per_iteration = K_;
   }
   else if (obj_ >= kHuber) h.objective = cfg_.objective;      // huber / fair / poisson / gamma / tweedie / regression_l1 / quantile / mape: the name alone
-  else if (obj_ == kCustom) h.objective = "";      // upstream writes no objective line without an objective function
+  else if (obj_ == kCustom) { h.objective = ""; h.num_class = K_; h.num_tree_per_iteration = K_; }      // no objective line without an objective function
   else h.objective = "lambdarank";
   h.average_output = boost_ == kRF;
   h.feature_names = ds_->feature_names;
@@ -1543,6 +1547,7 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     cfg_.objective = o;
   } else if (o.empty() || o.rfind("custom", 0) == 0) {
     obj_ = kCustom;      // trained with caller-supplied gradients: predictions are raw scores
+    K_ = std::max(1, loaded_header_.num_tree_per_iteration);
   } else {
     LGB_CHECK(o.rfind("regression", 0) == 0, "Model string: objective '%s' is not supported by this library", o.c_str());
     obj_ = kL2;

@@ -89,11 +89,13 @@ class LightGBMBooster:
             lib.LGBM_BoosterFree(other)
 
     def update_one_iteration_custom(self, gradient, hessian):
-        """updateOneIterationCustom (:371-392): one iteration from caller-supplied gradients (float32, one per training row)."""
-        g = np.ascontiguousarray(gradient, dtype=np.float32)
-        h = np.ascontiguousarray(hessian, dtype=np.float32)
-        if len(g) != self._train_rows or len(h) != self._train_rows:
-            raise ValueError("gradient / hessian must have one value per training row (%d)" % self._train_rows)
+        """updateOneIterationCustom (:371-392): one iteration from caller-supplied gradients (float32, one per training row and
+        class, class after class)."""
+        g = np.ascontiguousarray(gradient, dtype=np.float32).reshape(-1)
+        h = np.ascontiguousarray(hessian, dtype=np.float32).reshape(-1)
+        want = self._train_rows * self.num_classes()
+        if len(g) != want or len(h) != want:
+            raise ValueError("gradient / hessian must have one value per training row and class (%d)" % want)
         fin = C.c_int()
         validate(lightgbmlib().LGBM_BoosterUpdateOneIterCustom(self.booster_handle, g.ctypes.data_as(C.POINTER(C.c_float)),
                                                                h.ctypes.data_as(C.POINTER(C.c_float)), C.byref(fin)),

@@ -21,7 +21,9 @@ def update_one_iteration(train_params, booster, cur_iters):
     try:
         fobj = train_params.objectiveParams.fobj
         if fobj is not None:       # TrainUtils.scala:80-86: raw training scores -> user gradients -> UpdateOneIterCustom
-            gradient, hessian = fobj.get_gradient(booster.inner_predict(0).reshape(-1, 1), booster.train_dataset)
+            # innerPredict (LightGBMBooster.scala:316-330): [rows][classes] from the class-major native scores
+            k = booster.num_classes()
+            gradient, hessian = fobj.get_gradient(booster.inner_predict(0).reshape(k, -1).T, booster.train_dataset)
             return booster.update_one_iteration_custom(gradient, hessian)
         return booster.update_one_iteration()
     except Exception as e:  # noqa: BLE001 - mirrors the reference's catch-all

@@ -97,3 +97,57 @@ def test_estimator_with_fobj_learns_and_scores_raw(native):
     # same loss, same data: the custom model tracks the built-in one (it starts from 0 instead of the label average)
     rb = TextModel(builtin.getNativeModel()).predict_raw(X)
     assert np.corrcoef(raw, rb)[0, 1] > 0.98
+
+
+def test_custom_objective_with_several_classes(native, oracle):
+    """FObjTrait with a multiclass label (TrainUtils.scala:80-86 hands the [rows][classes] scores to the user and the returned arrays
+    — one value per row and class, class after class — to LGBM_BoosterUpdateOneIterCustom): num_class trees per iteration, no
+    objective line in the model.  Fed with the built-in softmax gradients the custom path grows the very same trees; with gradients
+    of its own it matches the oracle byte for byte."""
+    from helpers import oracle_dataset, strip_parameters
+    X, _ = S.higgs_shape(40000)
+    rng = np.random.Generator(np.random.PCG64(0))
+    y = np.digitize(X[:, 0] + 0.5 * X[:, 2] + 0.3 * rng.standard_normal(len(X)), [-0.6, 0.7]).astype(np.float32)
+    common = " num_class=3 num_leaves=15 max_bin=63 min_data_in_leaf=20 boost_from_average=false use_quantized_grad=true stochastic_rounding=false verbosity=-1"
+    nd = NativeDataset(X, y, "objective=multiclass" + common)
+    a = NativeBooster(nd, "objective=multiclass" + common)
+    b = NativeBooster(nd, "objective=custom" + common)
+    assert b.num_classes() == 3
+    for _ in range(5):
+        assert not a.update()
+        g, h = a.gradients()                    # [3][n], class-major
+        assert g.size == 3 * len(y)
+        assert not update_custom(b, g, h)
+    ma, mb = a.model(), b.model()
+    assert tree_blocks(ma) == tree_blocks(mb) and np.array_equal(a.scores(), b.scores())
+    assert "num_class=3" in mb and "num_tree_per_iteration=3" in mb and "\nobjective=" not in mb.split("Tree=0")[0]
+    a.free(); b.free()
+    # user gradients (one-vs-rest log-likelihood in numpy) against the oracle
+    params = "objective=custom" + common
+    nb = NativeBooster(nd, params)
+    _, dss, _ = oracle_dataset(oracle, X, y, params)
+    ob = oracle.Booster(dss, params)
+    for _ in range(4):
+        s = nb.scores().reshape(3, -1)
+        assert np.array_equal(s.reshape(-1), ob.scores())
+        prob = 1.0 / (1.0 + np.exp(-s))
+        onehot = (np.arange(3)[:, None] == y[None, :].astype(int))
+        g, h = (prob - onehot).astype(np.float32).reshape(-1), (prob * (1.0 - prob)).astype(np.float32).reshape(-1)
+        assert update_custom(nb, g, h) == ob.update_one_iter_custom(g, h)
+    assert strip_parameters(nb.model()) == strip_parameters(ob.save_model_to_string())
+    nb.free()
+    nd.free()
+
+    # through the estimator: a multiclass FObjTrait
+    class OneVsRest:
+        def get_gradient(self, predictions, training_data):
+            labels = training_data.get_label().astype(int)
+            assert predictions.shape == (len(labels), 3)
+            prob = 1.0 / (1.0 + np.exp(-predictions))
+            hot = np.arange(3)[None, :] == labels[:, None]
+            return (prob - hot).T.astype(np.float32).reshape(-1), (prob * (1.0 - prob)).T.astype(np.float32).reshape(-1)
+
+    model = LightGBMClassifier(objective="multiclass", fobj=OneVsRest(), numIterations=10, numLeaves=15, samplingMode="fixed").fit(
+        LocalDataFrame.from_arrays(X, y, num_partitions=2))
+    out = model.transform(X[:5000])
+    assert out["rawPrediction"].shape == (5000, 3) and (out["prediction"] == y[:5000]).mean() > 0.8
