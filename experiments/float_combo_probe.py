@@ -23,7 +23,7 @@ for seed in range(int(sys.argv[1]) if len(sys.argv) > 1 else 100):
     y = tc.labels_for(objective, z, rng)
     w = rng.uniform(0.5, 2.0, len(y)).astype(np.float32) if weighted else None
     query = None
-    if objective == "lambdarank":
+    if objective in ("lambdarank", "rank_xendcg"):
         sizes = []
         while sum(sizes) < len(y):
             sizes.append(int(rng.integers(5, 61)))

@@ -187,6 +187,7 @@ struct Config {
   // boosting = dart / goss (upstream config.h defaults)
   double drop_rate = 0.1, skip_drop = 0.5, top_rate = 0.2, other_rate = 0.1;
   int max_drop = 50, drop_seed = 4;
+  int objective_seed = 5;
   bool uniform_drop = false, xgboost_dart_mode = false;
   int num_machines = 1;
   int num_threads = 0;
@@ -317,6 +318,7 @@ struct Config {
       bagging_seed = r.NextShort(0, int_max);
       drop_seed = r.NextShort(0, int_max);
       feature_fraction_seed = r.NextShort(0, int_max);
+      objective_seed = r.NextShort(0, int_max);
     }
     getd("alpha", &alpha);
     getd("fair_c", &fair_c);
@@ -330,6 +332,7 @@ struct Config {
     geti("bagging_freq", &bagging_freq);
     geti("bagging_seed", &bagging_seed);
     getd("drop_rate", &drop_rate); getd("skip_drop", &skip_drop); getd("top_rate", &top_rate); getd("other_rate", &other_rate);
+    geti("objective_seed", &objective_seed);
     geti("max_drop", &max_drop); geti("drop_seed", &drop_seed); getb("uniform_drop", &uniform_drop); getb("xgboost_dart_mode", &xgboost_dart_mode);
     if (boosting == "random_forest") boosting = "rf";
     if (boosting == "gbrt") boosting = "gbdt";
@@ -357,6 +360,7 @@ struct Config {
     if (objective == "softmax") objective = "multiclass";
     if (objective == "l1" || objective == "mean_absolute_error" || objective == "mae") objective = "regression_l1";
     if (objective == "mean_absolute_percentage_error") objective = "mape";
+    if (objective == "xendcg" || objective == "xe_ndcg" || objective == "xe_ndcg_mart" || objective == "xendcg_mart") objective = "rank_xendcg";
   }
 };
 

@@ -471,7 +471,8 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA, OBJ_XENDCG } obj = OBJ_L2;
+  std::vector<std::vector<Random>> xe_rands;      // rank_xendcg: per shard, one stream per query (seeded objective_seed + query)
   std::vector<int> mono_inner;             // monotone direction per inner feature (empty: no constraints at all)
   bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA || (obj == OBJ_CUSTOM && K > 1); }
   std::vector<double> ova_label_weights, ova_suml;      // multiclassova: per class [neg, pos] label weights and the weighted positives
@@ -893,6 +894,15 @@ class Booster {
           sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
         }
       }
+    } else if (cfg.objective == "rank_xendcg") {
+      // RankXENDCG::Init (upstream src/objective/rank_objective.hpp): one random stream per query of the machine
+      obj = OBJ_XENDCG;
+      for (auto& sh : shards) {
+        if (sh.ds->query_boundaries.size() < 2) throw std::runtime_error("oracle: rank_xendcg needs query information");
+        std::vector<Random> r;
+        for (size_t q = 0; q + 1 < sh.ds->query_boundaries.size(); ++q) r.emplace_back(cfg.objective_seed + static_cast<int>(q));
+        xe_rands.push_back(std::move(r));
+      }
     } else if (cfg.objective == "lambdarank") {
       obj = OBJ_LAMBDARANK;
       label_gain = cfg.label_gain;
@@ -1081,6 +1091,56 @@ class Booster {
             const int sg = (diff > 0) - (diff < 0);
             sh.grad[i] = static_cast<score_t>(sg * (*lw)[i]);
             sh.hess[i] = has_weights ? d->weight[i] : 1.0f;
+          }
+        }
+      } else if (obj == OBJ_XENDCG) {
+        // RankXENDCG::GetGradientsForOneQuery: cross-entropy between the softmax of the scores and a randomly perturbed ground-truth
+        // distribution (2^label - uniform draw), with the first three terms of the expansion; exp is the software function both sides
+        // share, the sums run in document order
+        const int nq = static_cast<int>(d->query_boundaries.size()) - 1;
+#pragma omp parallel for schedule(guided)
+        for (int q = 0; q < nq; ++q) {
+          const int start = d->query_boundaries[q];
+          const int cnt = d->query_boundaries[q + 1] - start;
+          score_t* lambdas = sh.grad.data() + start;
+          score_t* hessians = sh.hess.data() + start;
+          if (cnt <= 1) { for (int i = 0; i < cnt; ++i) { lambdas[i] = 0.0f; hessians[i] = 0.0f; } continue; }
+          const double* score = sh.score.data() + start;
+          std::vector<double> rho(cnt), par(cnt);
+          double wmax = score[0];
+          for (int i = 1; i < cnt; ++i) wmax = std::max(score[i], wmax);
+          double wsum = 0.0;
+          for (int i = 0; i < cnt; ++i) { rho[i] = SoftExp(score[i] - wmax); wsum += rho[i]; }
+          for (int i = 0; i < cnt; ++i) rho[i] /= wsum;
+          double inv_denominator = 0;
+          for (int i = 0; i < cnt; ++i) {
+            par[i] = static_cast<double>(1 << static_cast<int>(d->label[start + i])) - xe_rands[s][q].NextFloat();      // Phi
+            inv_denominator += par[i];
+          }
+          inv_denominator = 1. / std::max<double>(kEpsilon, inv_denominator);
+          double sum_l1 = 0.0;
+          for (int i = 0; i < cnt; ++i) {
+            const double term = -par[i] * inv_denominator + rho[i];
+            lambdas[i] = static_cast<score_t>(term);
+            par[i] = term / (1. - rho[i]);
+            sum_l1 += par[i];
+          }
+          double sum_l2 = 0.0;
+          for (int i = 0; i < cnt; ++i) {
+            const double term = rho[i] * (sum_l1 - par[i]);
+            lambdas[i] += static_cast<score_t>(term);
+            par[i] = term / (1. - rho[i]);
+            sum_l2 += par[i];
+          }
+          for (int i = 0; i < cnt; ++i) {
+            lambdas[i] += static_cast<score_t>(rho[i] * (sum_l2 - par[i]));
+            hessians[i] = static_cast<score_t>(rho[i] * (1.0 - rho[i]));
+          }
+          if (has_weights) {
+            for (int j = 0; j < cnt; ++j) {
+              lambdas[j] = static_cast<score_t>(lambdas[j] * d->weight[start + j]);
+              hessians[j] = static_cast<score_t>(hessians[j] * d->weight[start + j]);
+            }
           }
         }
       } else if (obj != OBJ_LAMBDARANK) {
@@ -1675,6 +1735,7 @@ class Booster {
     if (obj == OBJ_MULTICLASS) return "multiclass num_class:" + std::to_string(K);
     if (obj == OBJ_MULTICLASSOVA) return "multiclassova num_class:" + std::to_string(K) + " sigmoid:" + FmtG(cfg.sigmoid);
     if (RenewsLeaves()) return cfg.objective;
+    if (obj == OBJ_XENDCG) return "rank_xendcg";
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }

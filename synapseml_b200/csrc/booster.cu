@@ -541,6 +541,20 @@ void Booster::InitObjective() {
       class_init_probs_[k] = acc[k] / acc[K_];
       if (std::fabs(class_init_probs_[k]) <= kEpsD || std::fabs(class_init_probs_[k]) >= 1.0 - kEpsD) class_need_train_[k] = 0;
     }
+  } else if (cfg_.objective == "rank_xendcg") {
+    // RankXENDCG::Init (upstream rank_objective.hpp): one random stream per query of this machine, seeded objective_seed + query
+    obj_ = kXendcg;
+    LGB_CHECK(!ds_->query_boundaries.empty(), "rank_xendcg needs query information (a group column)");
+    const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
+    std::vector<unsigned int> st(std::max(nq, 1));
+    max_query_len_ = 1;
+    for (int q = 0; q < nq; ++q) {
+      st[q] = static_cast<unsigned int>(cfg_.objective_seed + q);
+      max_query_len_ = std::max(max_query_len_, ds_->query_boundaries[q + 1] - ds_->query_boundaries[q]);
+    }
+    for (float l : label) LGB_CHECK(l >= 0 && l < 31 && l == static_cast<int>(l), "rank_xendcg labels must be integers in [0, 31)");
+    d_xe_rand_.Alloc(st.size());
+    LGB_CUDA(cudaMemcpy(d_xe_rand_.p, st.data(), sizeof(unsigned int) * st.size(), cudaMemcpyHostToDevice));
   } else if (cfg_.objective == "multiclassova") {
     // MulticlassOVA::Init: one BinaryLogloss per class whose positives are the rows of that class (label counts, is_unbalance /
     // scale_pos_weight weights and the sums behind BoostFromScore, all over all machines)
@@ -577,7 +591,7 @@ void Booster::InitObjective() {
     LGB_CHECK(K_ <= kMaxClasses, "num_class=%d is above %d", K_, kMaxClasses);
     if (K_ > 1) class_need_train_.assign(K_, 1);
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, multiclassova, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, multiclassova, rank_xendcg, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
   }
 }
 
@@ -603,6 +617,16 @@ void Booster::ComputeGradients(const double* score_override) {
   const float* w = has_weights_ ? ds_->d_weight.p : nullptr;
   if (obj_ == kMulticlass) {
     k_grad_multiclass<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[0].p, d_hess_[0].p, n, K_, static_cast<double>(K_) / (K_ - 1.0f));
+  } else if (obj_ == kXendcg) {
+    XendcgArgs a;
+    a.score = score; a.label = ds_->d_label.p; a.weight = w; a.qb = ds_->d_query_boundaries.p; a.rand_state = d_xe_rand_.p;
+    a.grad = d_grad_[grad_cur_].p; a.hess = d_hess_[grad_cur_].p; a.max_cnt = max_query_len_;
+    const size_t smem = static_cast<size_t>(max_query_len_) * 2 * sizeof(double);
+    LGB_CHECK(smem <= 200 * 1024, "rank_xendcg: a query with %d documents does not fit the kernel's shared memory", max_query_len_);
+    static size_t smem_set = 0;
+    if (smem > smem_set) { smem_set = smem; SetSmem(k_grad_xendcg, smem_set); }
+    const int nq = static_cast<int>(ds_->query_boundaries.size()) - 1;
+    if (nq > 0) k_grad_xendcg<<<nq, 256, smem, stream_>>>(a);
   } else if (obj_ == kMulticlassOva) {
     for (int k = 0; k < K_; ++k)
       k_grad_binary<<<grid, 256, 0, stream_>>>(score + static_cast<size_t>(k) * n_, ds_->d_label.p, w, d_grad_[0].p + static_cast<size_t>(k) * n_,
@@ -1291,7 +1315,7 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
   // ObtainAutomaticInitialScore (upstream src/boosting/gbdt.cpp): the objective's BoostFromScore over the labels of all machines,
   // then the mean over machines of what are identical values
   auto automatic_init_score = [&]() -> double {
-    if (obj_ == kLambdarank || obj_ == kCustom) return 0.0;
+    if (obj_ == kLambdarank || obj_ == kXendcg || obj_ == kCustom) return 0.0;
     double v;
     if (obj_ == kMulticlass) {
       v = std::log(std::max<double>(kEps, class_init_probs_[cls_]));
@@ -1527,8 +1551,8 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     obj_ = kBinary;
     const size_t p = o.find("sigmoid:");
     if (p != std::string::npos) cfg_.sigmoid = strtod(o.c_str() + p + 8, nullptr);
-  } else if (o.rfind("lambdarank", 0) == 0) {
-    obj_ = kLambdarank;
+  } else if (o.rfind("lambdarank", 0) == 0 || o.rfind("rank_xendcg", 0) == 0) {
+    obj_ = kLambdarank;      // (scoring only: both ranking objectives leave the raw score as the prediction)
   } else if (o.rfind("multiclassova", 0) == 0) {
     obj_ = kMulticlassOva;
     K_ = loaded_header_.num_tree_per_iteration;

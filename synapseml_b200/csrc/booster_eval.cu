@@ -38,7 +38,7 @@ void Booster::InitMetrics() {
     }
   }
   if (names.empty() && obj_ != kCustom)      // the objective's default; a custom objective has none
-    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : obj_ == kLambdarank ? "ndcg" : (obj_ == kMulticlass || obj_ == kMulticlassOva) ? "multi_logloss"
+    names.push_back(obj_ == kBinary ? "binary_logloss" : obj_ == kL2 ? "l2" : (obj_ == kLambdarank || obj_ == kXendcg) ? "ndcg" : (obj_ == kMulticlass || obj_ == kMulticlassOva) ? "multi_logloss"
                     : cfg_.objective);
   for (const std::string& m : names) {
     if (m == "None" || m == "none" || m == "null" || m == "na" || m == "custom") continue;

@@ -129,11 +129,12 @@ void Config::Set(const std::string& params) {
     bagging_seed = r.NextShort(0, 32767);
     drop_seed = r.NextShort(0, 32767);
     feature_fraction_seed = r.NextShort(0, 32767);
+    objective_seed = r.NextShort(0, 32767);
   }
   GET_D(alpha); GET_D(fair_c); GET_D(poisson_max_delta_step); GET_D(tweedie_variance_power);
   GET_D(feature_fraction); GET_D(feature_fraction_bynode); GET_I(feature_fraction_seed);
   GET_D(bagging_fraction); GET_D(pos_bagging_fraction); GET_D(neg_bagging_fraction); GET_I(bagging_freq); GET_I(bagging_seed);
-  GET_D(drop_rate); GET_D(skip_drop); GET_D(top_rate); GET_D(other_rate); GET_I(max_drop); GET_I(drop_seed); GET_B(uniform_drop); GET_B(xgboost_dart_mode);
+  GET_D(drop_rate); GET_D(skip_drop); GET_D(top_rate); GET_D(other_rate); GET_I(max_drop); GET_I(drop_seed); GET_I(objective_seed); GET_B(uniform_drop); GET_B(xgboost_dart_mode);
   // SynapseML emits the pre-3.0 key `max_position` (RankerTrainParams.scala:28).  It is honoured as an alias of
   // lambdarank_truncation_level unless that key is given explicitly (documented choice).
   if (has("lambdarank_truncation_level")) lambdarank_truncation_level = static_cast<int>(ToDouble("lambdarank_truncation_level", kv["lambdarank_truncation_level"]));
@@ -156,6 +157,7 @@ void Config::Set(const std::string& params) {
   if (objective == "softmax") objective = "multiclass";
   if (objective == "l1" || objective == "mean_absolute_error" || objective == "mae") objective = "regression_l1";
   if (objective == "mean_absolute_percentage_error") objective = "mape";
+  if (objective == "xendcg" || objective == "xe_ndcg" || objective == "xe_ndcg_mart" || objective == "xendcg_mart") objective = "rank_xendcg";
   if (boosting == "random_forest") boosting = "rf";
   if (boosting == "gbrt") boosting = "gbdt";
 }

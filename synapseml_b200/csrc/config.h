@@ -57,6 +57,7 @@ struct Config {
   // boosting = dart / goss (upstream config.h defaults)
   double drop_rate = 0.1, skip_drop = 0.5, top_rate = 0.2, other_rate = 0.1;
   int max_drop = 50, drop_seed = 4;
+  int objective_seed = 5;      // rank_xendcg's per-query streams (LightGBMParams.scala objectiveSeed)
   bool uniform_drop = false, xgboost_dart_mode = false;
   int num_machines = 1;
   int num_threads = 0;

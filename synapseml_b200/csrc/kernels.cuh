@@ -289,6 +289,93 @@ __global__ void __launch_bounds__(256) k_grad_lambdarank(LambdarankArgs a) {
   }
 }
 
+// rank_xendcg (upstream RankXENDCG::GetGradientsForOneQuery): one CTA per query.  The ground-truth distribution is 2^label minus a
+// uniform draw from the QUERY's own LCG stream (one draw per document per call, in document order), the model's is the softmax of the
+// scores; gradient = the first three terms of the expansion, hessian = rho (1 - rho).  The element-wise parts run on all threads;
+// the draws and the four sums (softmax denominator, ground-truth denominator, first- and second-order sums) run on thread 0 in
+// document order, as the CPU loop does, so float32 results are bit-identical.  Shared: 3 doubles per document.
+struct XendcgArgs {
+  const double* score; const float* label; const float* weight; const int* qb; unsigned int* rand_state; float* grad; float* hess; int max_cnt;
+};
+__global__ void __launch_bounds__(256) k_grad_xendcg(XendcgArgs a) {
+  extern __shared__ __align__(16) unsigned char xe_smem[];
+  double* s_rho = reinterpret_cast<double*>(xe_smem);
+  double* s_par = s_rho + a.max_cnt;
+  __shared__ double s_red[8];
+  __shared__ double s_val;
+  const int q = blockIdx.x;
+  const int start = a.qb[q], cnt = a.qb[q + 1] - start;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (cnt <= 1) {
+    if (tid < cnt) { a.grad[start + tid] = 0.0f; a.hess[start + tid] = 0.0f; }
+    return;
+  }
+  // softmax: maximum (any order), exp, then the sum in document order
+  double wmax = -INFINITY;
+  for (int i = tid; i < cnt; i += blockDim.x) wmax = fmax(wmax, a.score[start + i]);
+  for (int o = 16; o > 0; o >>= 1) wmax = fmax(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+  if (lane == 0) s_red[warp] = wmax;
+  __syncthreads();
+  wmax = s_red[0];
+  #pragma unroll
+  for (int w = 1; w < 8; ++w) wmax = fmax(wmax, s_red[w]);
+  for (int i = tid; i < cnt; i += blockDim.x) s_rho[i] = SoftExp(a.score[start + i] - wmax);
+  __syncthreads();
+  if (tid == 0) {
+    double wsum = 0.0;
+    for (int i = 0; i < cnt; ++i) wsum += s_rho[i];
+    s_val = wsum;
+    // Phi(label, draw) and the ground-truth denominator
+    unsigned int x = a.rand_state[q];
+    double den = 0.0;
+    for (int i = 0; i < cnt; ++i) {
+      x = 214013u * x + 2531011u;
+      const float u = static_cast<float>((x >> 16) & 0x7FFF) / 32768.0f;
+      const double p = static_cast<double>(1 << static_cast<int>(a.label[start + i])) - u;
+      s_par[i] = p;
+      den += p;
+    }
+    a.rand_state[q] = x;
+    s_red[0] = 1. / fmax(KEPS, den);
+  }
+  __syncthreads();
+  const double wsum = s_val, inv_den = s_red[0];
+  __syncthreads();
+  float lam[8];      // this thread's documents tid, tid + 256, ... (queries of up to 2048 documents keep them in registers)
+  int nd = 0;
+  for (int i = tid; i < cnt; i += blockDim.x, ++nd) {
+    const double rho = s_rho[i] / wsum;
+    s_rho[i] = rho;
+    const double term = -s_par[i] * inv_den + rho;
+    if (nd < 8) lam[nd] = static_cast<float>(term); else a.grad[start + i] = static_cast<float>(term);
+    s_par[i] = term / (1. - rho);
+  }
+  __syncthreads();
+  if (tid == 0) { double s1 = 0.0; for (int i = 0; i < cnt; ++i) s1 += s_par[i]; s_val = s1; }
+  __syncthreads();
+  const double sum_l1 = s_val;
+  __syncthreads();
+  nd = 0;
+  for (int i = tid; i < cnt; i += blockDim.x, ++nd) {
+    const double term = s_rho[i] * (sum_l1 - s_par[i]);
+    if (nd < 8) lam[nd] += static_cast<float>(term); else a.grad[start + i] += static_cast<float>(term);
+    s_par[i] = term / (1. - s_rho[i]);
+  }
+  __syncthreads();
+  if (tid == 0) { double s2 = 0.0; for (int i = 0; i < cnt; ++i) s2 += s_par[i]; s_val = s2; }
+  __syncthreads();
+  const double sum_l2 = s_val;
+  nd = 0;
+  for (int i = tid; i < cnt; i += blockDim.x, ++nd) {
+    const double rho = s_rho[i];
+    float g = nd < 8 ? lam[nd] : a.grad[start + i];
+    g += static_cast<float>(rho * (sum_l2 - s_par[i]));
+    float h = static_cast<float>(rho * (1.0 - rho));
+    if (a.weight != nullptr) { g = static_cast<float>(g * a.weight[start + i]); h = static_cast<float>(h * a.weight[start + i]); }
+    a.grad[start + i] = g; a.hess[start + i] = h;
+  }
+}
+
 __global__ void k_add_constant(double* score, int n, double v) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] += v;
 }

@@ -36,7 +36,7 @@ def random_combo(seed):
     r = np.random.Generator(np.random.PCG64(1000 + seed))
     pick = lambda *xs: xs[int(r.integers(0, len(xs)))]
     objective = pick("binary", "regression", "multiclass", "regression_l1", "multiclassova", "huber", "lambdarank", "poisson", "quantile", "fair",
-                     "tweedie", "mape", "gamma")
+                     "tweedie", "mape", "gamma", "rank_xendcg")
     boosting = pick("gbdt", "gbdt", "gbdt", "rf", "dart", "goss")
     p = ["objective=" + objective, "num_leaves=%d" % pick(7, 15, 31), "max_bin=%d" % pick(15, 63, 255, 600), "min_data_in_leaf=%d" % pick(5, 20, 60),
          "learning_rate=%s" % pick("0.1", "0.3")]
@@ -76,7 +76,7 @@ def labels_for(objective, z, rng):
         return np.digitize(z + rng.normal(0, 0.3, len(z)), [-0.8, 0.9]).astype(np.float32)
     if objective == "binary":
         return (z + rng.normal(0, 0.5, len(z)) > 0).astype(np.float32)
-    if objective == "lambdarank":
+    if objective in ("lambdarank", "rank_xendcg"):
         return np.digitize(z + rng.normal(0, 0.5, len(z)), [-0.5, 0.8, 2.0]).astype(np.float32)       # relevance 0..3
     if objective in ("poisson", "tweedie"):
         return rng.poisson(np.exp(np.clip(0.4 * z, -3, 2))).astype(np.float32)
@@ -92,10 +92,10 @@ def test_random_option_combinations_are_byte_identical(native, oracle, seed):
     y = labels_for(objective, z, rng)
     w = rng.uniform(0.5, 2.0, len(y)).astype(np.float32) if weighted else None
     query = None
-    if objective == "lambdarank":       # queries of 5..60 documents, contiguous
+    if objective in ("lambdarank", "rank_xendcg"):       # queries of 1..60 documents, contiguous
         sizes = []
         while sum(sizes) < len(y):
-            sizes.append(int(rng.integers(5, 61)))
+            sizes.append(int(rng.integers(1, 61)))
         query = np.repeat(np.arange(len(sizes)), sizes)[:len(y)].astype(np.int32)
     nd = NativeDataset(X, y, params, weight=w, query=query, micro_batches=[4096, 100])
     nb = NativeBooster(nd, params)

@@ -100,6 +100,21 @@ def test_ranker_group_column_types(native):
         LightGBMRanker(numIterations=1).fit(LocalDataFrame.from_arrays(X, rel, num_partitions=1, group=qid.astype(np.float64)))
 
 
+def test_ranker_with_rank_xendcg_and_objective_seed(native):
+    """objective=rank_xendcg with objectiveSeed (LightGBMParams.scala:441-445 exists for this objective alone): the per-query random
+    streams make the model depend on the seed, and reproducible for a given one."""
+    X, rel, qid = S.mslr_shape(12000, f=20)
+    df = LocalDataFrame.from_arrays(X, rel, num_partitions=1, group=qid.astype(np.int32))
+    kw = dict(objective="rank_xendcg", numIterations=6, numLeaves=15, minDataInLeaf=10, evalAt=[1, 3], isProvideTrainingMetric=True)
+    est = LightGBMRanker(objectiveSeed=7, **kw)
+    a = est.fit(df).getNativeModel()
+    assert "objective=rank_xendcg" in a and "[objective_seed: 7]" in a
+    assert a == LightGBMRanker(objectiveSeed=7, **kw).fit(df).getNativeModel()
+    assert a.split("parameters:")[0] != LightGBMRanker(objectiveSeed=8, **kw).fit(df).getNativeModel().split("parameters:")[0]
+    hist = est.performance_measures["evalHistory"]
+    assert hist[-1][0]["ndcg@3"] > hist[0][0]["ndcg@3"] > 0.3          # the default metric of the objective is ndcg, and it improves
+
+
 def test_unsupported_options_fail_loudly(native):
     X, y = S.higgs_shape(2000)
     df = LocalDataFrame.from_arrays(X, y)
