@@ -360,6 +360,7 @@ struct Config {
     if (objective == "softmax") objective = "multiclass";
     if (objective == "l1" || objective == "mean_absolute_error" || objective == "mae") objective = "regression_l1";
     if (objective == "mean_absolute_percentage_error") objective = "mape";
+    if (objective == "xentropy") objective = "cross_entropy";
     if (objective == "xendcg" || objective == "xe_ndcg" || objective == "xe_ndcg_mart" || objective == "xendcg_mart") objective = "rank_xendcg";
   }
 };

@@ -471,7 +471,7 @@ class Booster {
   std::vector<std::unique_ptr<Tree>> models;
   int iter = 0;
   // objective state
-  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA, OBJ_XENDCG } obj = OBJ_L2;
+  enum Obj { OBJ_BINARY, OBJ_L2, OBJ_LAMBDARANK, OBJ_HUBER, OBJ_FAIR, OBJ_POISSON, OBJ_GAMMA, OBJ_TWEEDIE, OBJ_CUSTOM, OBJ_MULTICLASS, OBJ_L1, OBJ_QUANTILE, OBJ_MAPE, OBJ_MULTICLASSOVA, OBJ_XENDCG, OBJ_XENTROPY } obj = OBJ_L2;
   std::vector<std::vector<Random>> xe_rands;      // rank_xendcg: per shard, one stream per query (seeded objective_seed + query)
   std::vector<int> mono_inner;             // monotone direction per inner feature (empty: no constraints at all)
   bool IsMulti() const { return obj == OBJ_MULTICLASS || obj == OBJ_MULTICLASSOVA || (obj == OBJ_CUSTOM && K > 1); }
@@ -894,6 +894,9 @@ class Booster {
           sh.hess_k.assign(K, std::vector<score_t>(n, 0.0f));
         }
       }
+    } else if (cfg.objective == "cross_entropy") {
+      obj = OBJ_XENTROPY;      // CrossEntropy (upstream src/objective/xentropy_objective.hpp): labels are probabilities in [0, 1]
+      for (auto& sh : shards) for (float l : sh.ds->label) if (!(l >= 0.0f && l <= 1.0f)) throw std::runtime_error("oracle: cross_entropy needs labels in [0, 1]");
     } else if (cfg.objective == "rank_xendcg") {
       // RankXENDCG::Init (upstream src/objective/rank_objective.hpp): one random stream per query of the machine
       obj = OBJ_XENDCG;
@@ -966,6 +969,17 @@ class Booster {
       pavg = std::min(pavg, 1.0 - kEpsilon);
       pavg = std::max<double>(pavg, kEpsilon);
       return std::log(pavg / (1.0f - pavg)) / cfg.sigmoid;
+    }
+    if (obj == OBJ_XENTROPY) {      // CrossEntropy::BoostFromScore
+      for (auto& sh : shards) {
+        const Dataset* d = sh.ds;
+        if (has_weights) { for (int64_t i = 0; i < d->num_data; ++i) { suml += d->label[i] * d->weight[i]; sumw += d->weight[i]; } }
+        else { sumw += static_cast<double>(d->num_data); for (int64_t i = 0; i < d->num_data; ++i) suml += d->label[i]; }
+      }
+      double pavg = suml / sumw;
+      pavg = std::min(pavg, 1.0 - kEpsilon);
+      pavg = std::max<double>(pavg, kEpsilon);
+      return std::log(pavg / (1.0f - pavg));
     }
     if (obj == OBJ_BINARY) {
       for (auto& sh : shards) {
@@ -1091,6 +1105,18 @@ class Booster {
             const int sg = (diff > 0) - (diff < 0);
             sh.grad[i] = static_cast<score_t>(sg * (*lw)[i]);
             sh.hess[i] = has_weights ? d->weight[i] : 1.0f;
+          }
+        }
+      } else if (obj == OBJ_XENTROPY) {      // CrossEntropy::GetGradients
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+          const double z = 1.0f / (1.0f + SoftExp(-sh.score[i]));
+          if (!has_weights) {
+            sh.grad[i] = static_cast<score_t>(z - d->label[i]);
+            sh.hess[i] = static_cast<score_t>(z * (1.0f - z));
+          } else {
+            sh.grad[i] = static_cast<score_t>((z - d->label[i]) * d->weight[i]);
+            sh.hess[i] = static_cast<score_t>(z * (1.0f - z) * d->weight[i]);
           }
         }
       } else if (obj == OBJ_XENDCG) {
@@ -1736,6 +1762,7 @@ class Booster {
     if (obj == OBJ_MULTICLASSOVA) return "multiclassova num_class:" + std::to_string(K) + " sigmoid:" + FmtG(cfg.sigmoid);
     if (RenewsLeaves()) return cfg.objective;
     if (obj == OBJ_XENDCG) return "rank_xendcg";
+    if (obj == OBJ_XENTROPY) return "cross_entropy";
     if (obj != OBJ_LAMBDARANK) return cfg.objective;      // huber / fair / poisson / gamma / tweedie: the name alone
     return "lambdarank";
   }

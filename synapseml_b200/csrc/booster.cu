@@ -541,6 +541,10 @@ void Booster::InitObjective() {
       class_init_probs_[k] = acc[k] / acc[K_];
       if (std::fabs(class_init_probs_[k]) <= kEpsD || std::fabs(class_init_probs_[k]) >= 1.0 - kEpsD) class_need_train_[k] = 0;
     }
+  } else if (cfg_.objective == "cross_entropy") {
+    obj_ = kXentropy;      // CrossEntropy (upstream xentropy_objective.hpp): labels are probabilities in [0, 1]
+    static_assert(kXentropy == 15, "k_grad_point's kind for cross_entropy");
+    for (float l : label) LGB_CHECK(l >= 0.0f && l <= 1.0f, "objective=cross_entropy needs labels in [0, 1]");
   } else if (cfg_.objective == "rank_xendcg") {
     // RankXENDCG::Init (upstream rank_objective.hpp): one random stream per query of this machine, seeded objective_seed + query
     obj_ = kXendcg;
@@ -591,7 +595,7 @@ void Booster::InitObjective() {
     LGB_CHECK(K_ <= kMaxClasses, "num_class=%d is above %d", K_, kMaxClasses);
     if (K_ > 1) class_need_train_.assign(K_, 1);
   } else {
-    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, multiclass, multiclassova, rank_xendcg, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
+    throw std::runtime_error("objective=" + cfg_.objective + " is not supported by this library yet (binary, cross_entropy, multiclass, multiclassova, rank_xendcg, regression, regression_l1, quantile, mape, huber, fair, poisson, gamma, tweedie, lambdarank, custom)");
   }
 }
 
@@ -637,7 +641,7 @@ void Booster::ComputeGradients(const double* score_override) {
     k_grad_binary<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, cfg_.sigmoid, label_weights_[0], label_weights_[1]);
   } else if (obj_ == kL2) {
     k_grad_l2<<<grid, 256, 0, stream_>>>(score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n);
-  } else if (obj_ >= kHuber) {
+  } else if (obj_ >= kHuber) {      // (kXentropy included: kind 15 of k_grad_point)
     const double p0 = (obj_ == kHuber || obj_ == kQuantile) ? cfg_.alpha : obj_ == kFair ? cfg_.fair_c
                       : obj_ == kPoisson ? SoftExp(cfg_.poisson_max_delta_step) : cfg_.tweedie_variance_power;
     k_grad_point<<<grid, 256, 0, stream_>>>(static_cast<int>(obj_), score, ds_->d_label.p, w, d_grad_[grad_cur_].p, d_hess_[grad_cur_].p, n, p0,
@@ -1333,11 +1337,11 @@ bool Booster::TrainOneIter(const float* custom_grad, const float* custom_hess) {
       double sums[2];
       BoostFromScoreLocalSums(&sums[0], &sums[1]);
       net_->HostAllReduceSum(sums, 2);
-      if (obj_ == kBinary) {
+      if (obj_ == kBinary || obj_ == kXentropy) {      // (cross_entropy: the mean label, no sigmoid parameter)
         double pavg = sums[0] / sums[1];
         pavg = std::min(pavg, 1.0 - kEps);
         pavg = std::max<double>(pavg, kEps);
-        v = std::log(pavg / (1.0f - pavg)) / cfg_.sigmoid;
+        v = std::log(pavg / (1.0f - pavg)) / (obj_ == kBinary ? cfg_.sigmoid : 1.0);
       } else {
         v = sums[0] / sums[1];
         if (LogLink()) v = v > 0.0 ? std::log(v) : -std::numeric_limits<double>::infinity();      // Common::SafeLog of the mean label
@@ -1563,6 +1567,9 @@ Booster::Booster(const std::string& model_str) : ds_(nullptr) {
     obj_ = kMulticlass;
     K_ = loaded_header_.num_tree_per_iteration;
     LGB_CHECK(K_ >= 2 && K_ == loaded_header_.num_class, "Model string: multiclass needs num_tree_per_iteration == num_class >= 2");
+  } else if (o == "cross_entropy") {
+    obj_ = kXentropy;
+    cfg_.objective = o;
   } else if (o == "huber" || o == "fair" || o == "poisson" || o == "gamma" || o == "tweedie") {
     obj_ = o == "huber" ? kHuber : o == "fair" ? kFair : o == "poisson" ? kPoisson : o == "gamma" ? kGamma : kTweedie;
     cfg_.objective = o;
@@ -1729,7 +1736,7 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
   const int64_t chunk_rows = row_major ? std::max<int64_t>(1, std::min<int64_t>(nrow, (int64_t(256) << 20) / (esz * ncol))) : nrow;
   dp_in_.Reserve(static_cast<size_t>(chunk_rows) * ncol * esz);
   dp_out_.Reserve(static_cast<size_t>(chunk_rows) * per_row);
-  const int sig_on = (obj_ == kBinary || obj_ == kMulticlassOva) ? 1 : LogLink() ? 2 : obj_ == kMulticlass ? 3 : 0;      // ConvertOutput: sigmoid, exp, softmax or none
+  const int sig_on = (obj_ == kBinary || obj_ == kMulticlassOva || obj_ == kXentropy) ? 1 : LogLink() ? 2 : obj_ == kMulticlass ? 3 : 0;      // ConvertOutput: sigmoid, exp, softmax or none
   for (int64_t r0 = 0; r0 < nrow; r0 += chunk_rows) {
     const int64_t nr = std::min(chunk_rows, nrow - r0);
     const unsigned char* src = static_cast<const unsigned char*>(data) + (row_major ? static_cast<size_t>(r0) * ncol * esz : 0);
@@ -1748,10 +1755,10 @@ void Booster::PredictForMat(const void* data, int data_type, int64_t nrow, int n
                                                              reinterpret_cast<ShapPathElement*>(dp_paths_.p), path_elems, dp_out_.p);
     } else if (data_type == 1)
       k_predict<double><<<grid, 128, 0, stream_>>>(reinterpret_cast<const double*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, boost_ == kRF ? (t1 - t0) / K_ : 0, predict_type, sig_on,
-                                                   cfg_.sigmoid, dp_out_.p);
+                                                   obj_ == kXentropy ? 1.0 : cfg_.sigmoid, dp_out_.p);
     else
       k_predict<float><<<grid, 128, 0, stream_>>>(reinterpret_cast<const float*>(dp_in_.p), nr, rs, cs, m, t0, t1, K_, boost_ == kRF ? (t1 - t0) / K_ : 0, predict_type, sig_on,
-                                                  cfg_.sigmoid, dp_out_.p);
+                                                  obj_ == kXentropy ? 1.0 : cfg_.sigmoid, dp_out_.p);
     LGB_CUDA(cudaGetLastError());
     LGB_CUDA(cudaMemcpyAsync(out + static_cast<size_t>(r0) * per_row, dp_out_.p, sizeof(double) * nr * per_row, cudaMemcpyDeviceToHost, stream_));
     LGB_CUDA(cudaStreamSynchronize(stream_));

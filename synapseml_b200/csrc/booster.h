@@ -189,7 +189,7 @@ class Booster {
   int64_t n_ = 0, n_global_ = 0, row_offset_ = 0;
   int F_ = 0;
   int iter_ = 0;
-  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass, kL1, kQuantile, kMape, kMulticlassOva, kXendcg } obj_ = kL2;
+  enum Obj { kBinary, kL2, kLambdarank, kCustom, kHuber, kFair, kPoisson, kGamma, kTweedie, kMulticlass, kL1, kQuantile, kMape, kMulticlassOva, kXendcg, kXentropy } obj_ = kL2;
   DevBuf<unsigned int> d_xe_rand_;      // rank_xendcg: the LCG state of every query's stream
   bool PointRegression() const { return obj_ == kL2 || (obj_ >= kHuber && obj_ <= kTweedie) || RenewsLeaves(); }
   // l1 / quantile / mape (upstream IsRenewTreeOutput): every leaf's output is re-fit as a percentile of the residuals of its rows

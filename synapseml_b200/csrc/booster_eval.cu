@@ -18,7 +18,7 @@ namespace lgb {
 namespace {
 constexpr int kNumSms = 148;
 enum { kEvLogloss = 0, kEvError = 1, kEvL2 = 2, kEvRmse = 3, kEvAuc = 4, kEvNdcg = 5, kEvHuber = 6, kEvFair = 7, kEvPoisson = 8, kEvGamma = 9,
-       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15, kEvGammaDeviance = 16, kEvMap = 17 };   // (Booster has its own kL2: distinct names)
+       kEvTweedie = 10, kEvMultiLogloss = 11, kEvMultiError = 12, kEvL1 = 13, kEvQuantile = 14, kEvMape = 15, kEvGammaDeviance = 16, kEvMap = 17, kEvXentropy = 18 };   // (Booster has its own kL2: distinct names)
 }
 
 void Booster::InitMetrics() {
@@ -56,6 +56,7 @@ void Booster::InitMetrics() {
     else if (m == "quantile") metrics_.push_back({kEvQuantile, "quantile"});
     else if (m == "mape" || m == "mean_absolute_percentage_error") metrics_.push_back({kEvMape, "mape"});
     else if (m == "gamma_deviance" || m == "gamma-deviance") metrics_.push_back({kEvGammaDeviance, "gamma_deviance"});
+    else if (m == "cross_entropy" || m == "xentropy") metrics_.push_back({kEvXentropy, "cross_entropy"});
     else if (m == "multi_logloss" || m == "multiclass" || m == "softmax" || m == "multiclassova" || m == "multiclass_ova" || m == "ova" || m == "ovr") metrics_.push_back({kEvMultiLogloss, "multi_logloss"});
     else if (m == "multi_error") metrics_.push_back({kEvMultiError, "multi_error"});
     else if (m == "ndcg" || m == "lambdarank" || m == "rank_xendcg" || m == "xendcg") {

@@ -84,7 +84,11 @@ __global__ void k_grad_point(int kind, const double* __restrict__ score, const f
     const double sc = score[i];
     const double y = label[i];
     double g, h;
-    if (kind >= 10) {
+    if (kind == 15) {           // cross_entropy (upstream xentropy_objective.hpp): labels are probabilities
+      const double z = 1.0f / (1.0f + SoftExp(-sc));
+      g = z - y;
+      h = z * (1.0f - z);
+    } else if (kind >= 10) {
       const double diff = sc - y;
       if (kind == 10) {
         g = SignD(diff);

@@ -17,7 +17,7 @@ constexpr int kMetricBlocks = 592;
 constexpr int kMetricThreads = 256;
 
 enum PointMetric { kMetricBinaryLogloss = 0, kMetricBinaryError = 1, kMetricL2 = 2, kMetricHuber = 3, kMetricFair = 4, kMetricPoisson = 5,
-                   kMetricGamma = 6, kMetricTweedie = 7, kMetricL1 = 8, kMetricQuantile = 9, kMetricMape = 10, kMetricGammaDeviance = 11 };
+                   kMetricGamma = 6, kMetricTweedie = 7, kMetricL1 = 8, kMetricQuantile = 9, kMetricMape = 10, kMetricGammaDeviance = 11, kMetricXentropy = 13 };
 
 __device__ __forceinline__ double BlockSumD(double v, double* s_w /*[8]*/) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -69,6 +69,11 @@ __global__ void __launch_bounds__(kMetricThreads) k_metric_point(const double* _
         loss = delta < 0 ? (p0 - 1.0f) * delta : p0 * delta;
       } else if (kind == kMetricMape) {
         loss = fabs(lab - t) / fmax(1.0, fabs(lab));
+      } else if (kind == kMetricXentropy) {       // CrossEntropyMetric: XentLoss(label, sigmoid(score)), logs clipped at 1e-12
+        const double p = 1.0 / (1.0 + exp(-s));
+        const double a = lab * (p > 1.0e-12 ? log(p) : log(1.0e-12));
+        const double b = (1.0f - lab) * (1.0f - p > 1.0e-12 ? log(1.0f - p) : log(1.0e-12));
+        loss = -(a + b);
       } else if (kind == kMetricGammaDeviance) {  // GammaDevianceMetric::LossOnPoint
         const double tmp = lab / (t + 1.0e-9);
         loss = tmp - (tmp > 0.0 ? log(tmp) : -INFINITY) - 1;

@@ -36,7 +36,7 @@ def random_combo(seed):
     r = np.random.Generator(np.random.PCG64(1000 + seed))
     pick = lambda *xs: xs[int(r.integers(0, len(xs)))]
     objective = pick("binary", "regression", "multiclass", "regression_l1", "multiclassova", "huber", "lambdarank", "poisson", "quantile", "fair",
-                     "tweedie", "mape", "gamma", "rank_xendcg")
+                     "tweedie", "mape", "gamma", "rank_xendcg", "cross_entropy")
     boosting = pick("gbdt", "gbdt", "gbdt", "rf", "dart", "goss")
     p = ["objective=" + objective, "num_leaves=%d" % pick(7, 15, 31), "max_bin=%d" % pick(15, 63, 255, 600), "min_data_in_leaf=%d" % pick(5, 20, 60),
          "learning_rate=%s" % pick("0.1", "0.3")]
@@ -78,6 +78,8 @@ def labels_for(objective, z, rng):
         return (z + rng.normal(0, 0.5, len(z)) > 0).astype(np.float32)
     if objective in ("lambdarank", "rank_xendcg"):
         return np.digitize(z + rng.normal(0, 0.5, len(z)), [-0.5, 0.8, 2.0]).astype(np.float32)       # relevance 0..3
+    if objective == "cross_entropy":
+        return np.clip(1.0 / (1.0 + np.exp(-z)) + rng.normal(0, 0.1, len(z)), 0.0, 1.0).astype(np.float32)      # probabilities as labels
     if objective in ("poisson", "tweedie"):
         return rng.poisson(np.exp(np.clip(0.4 * z, -3, 2))).astype(np.float32)
     if objective == "gamma":

@@ -119,7 +119,7 @@ def test_unsupported_options_fail_loudly(native):
     X, y = S.higgs_shape(2000)
     df = LocalDataFrame.from_arrays(X, y)
     from synapseml_b200.lightgbm.native import LightGBMNativeError
-    for kw in (dict(boostingType="plain"), dict(objective="cross_entropy"), dict(maxBin=100000), dict(passThroughArgs="feature_fraction_bynode=1.5"),
+    for kw in (dict(boostingType="plain"), dict(objective="cross_entropy_lambda"), dict(maxBin=100000), dict(passThroughArgs="feature_fraction_bynode=1.5"),
                dict(passThroughArgs="monotone_constraints=1,0,0")):
         with pytest.raises((LightGBMNativeError, NotImplementedError)):
             LightGBMClassifier(numIterations=1, **kw).fit(df)

@@ -103,6 +103,35 @@ def test_gamma_deviance_metric(native):
     nd.free()
 
 
+def test_cross_entropy_objective_and_metric(native, oracle):
+    """objective=cross_entropy (labels are probabilities; upstream xentropy_objective.hpp): byte-identical quantized model, sigmoid
+    output, metric = -(y log p + (1 - y) log(1 - p)) averaged."""
+    from helpers import oracle_dataset, strip_parameters
+    X, _ = count_data(20000, positive=False)
+    rng = np.random.Generator(np.random.PCG64(8))
+    y = np.clip(1.0 / (1.0 + np.exp(-X[:, 0])) + rng.normal(0, 0.1, len(X)), 0, 1).astype(np.float32)
+    params = "objective=cross_entropy num_leaves=15 max_bin=63 use_quantized_grad=true stochastic_rounding=false verbosity=-1"
+    nd = NativeDataset(X, y, params)
+    nb = NativeBooster(nd, params)
+    _, dss, _ = oracle_dataset(oracle, X, y, params)
+    ob = oracle.Booster(dss, params)
+    for _ in range(6):
+        assert nb.update() == ob.update_one_iter()
+    ms = nb.model()
+    assert strip_parameters(ms) == strip_parameters(ob.save_model_to_string()) and "objective=cross_entropy" in ms
+    n = C.c_int()
+    out = np.zeros(4)
+    validate(lightgbmlib().LGBM_BoosterGetEval(nb.handle, 0, C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+    p = 1.0 / (1.0 + np.exp(-nb.scores()))
+    assert n.value == 1 and np.isclose(out[0], -np.mean(y * np.log(p) + (1 - y) * np.log(1 - p)), rtol=1e-10)
+    from synapseml_b200.lightgbm.booster import LightGBMBooster
+    lb = LightGBMBooster(model_str=ms)
+    assert np.allclose(lb.predict_for_mat(X[:500], LightGBMBooster.PREDICT_NORMAL), p[:500], rtol=1e-12)
+    lb.free_native_memory()
+    nb.free()
+    nd.free()
+
+
 def test_regressor_estimator_with_tweedie(native):
     X, y = count_data(30000, positive=False)
     df = LocalDataFrame.from_arrays(X, y, num_partitions=2)
