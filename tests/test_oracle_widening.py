@@ -157,3 +157,42 @@ def test_balanced_bagging_keeps_the_two_fractions(oracle):
     in_bag = t.internal_count[0]                  # rows the root saw
     want = 0.9 * (y > 0).sum() + 0.3 * (y == 0).sum()
     assert abs(in_bag - want) < 4 * np.sqrt(len(y))
+
+
+def test_cross_entropy_closed_form(oracle):
+    # labels are probabilities; init = logit(mean label); at that score g = p - y, h = p (1 - p)
+    y = np.array([0.1, 0.9, 0.4, 0.6, 0.25, 0.75] * 20, dtype=np.float32)
+    X = np.random.Generator(np.random.PCG64(0)).normal(size=(len(y), 2))
+    bst, _ = oracle.fit(X, y, "objective=cross_entropy num_leaves=2 min_data_in_leaf=1000 verbosity=-1", num_iterations=1)
+    p = float(np.mean(y.astype(np.float64)))
+    assert np.allclose(bst.scores(), np.log(p / (1 - p)), atol=1e-12)
+    g, h = bst.gradients()
+    assert np.allclose(g, p - y, atol=1e-6) and np.allclose(h, p * (1 - p), atol=1e-6)
+
+
+def test_rank_xendcg_gradients_against_a_numpy_restatement(oracle):
+    # two queries (4 documents, 1 document); scores start at 0, so rho = 1 / 4.  The ground truth is 2^label - u with u drawn from the
+    # query's own LCG (x <- 214013 x + 2531011, u = ((x >> 16) & 0x7fff) / 32768, seeded objective_seed + query).
+    y = np.array([2.0, 0.0, 1.0, 0.0, 3.0], dtype=np.float32)
+    q = np.array([0, 0, 0, 0, 1], dtype=np.int32)
+    X = np.random.Generator(np.random.PCG64(0)).normal(size=(5, 2))
+    bst, _ = oracle.fit(X, y, "objective=rank_xendcg objective_seed=11 num_leaves=2 min_data_in_leaf=1000 verbosity=-1", num_iterations=1, query=q)
+    g, h = bst.gradients()
+    x = 11
+    us = []
+    for _ in range(4):
+        x = (214013 * x + 2531011) & 0xFFFFFFFF
+        us.append(np.float32(((x >> 16) & 0x7FFF)) / np.float32(32768.0))
+    par = np.array([2.0 ** l for l in y[:4]]) - np.array(us, dtype=np.float64)
+    rho = np.full(4, 0.25)
+    inv = 1.0 / par.sum()
+    t1 = -par * inv + rho
+    lam = t1.astype(np.float32)
+    p1 = t1 / (1 - rho)
+    t2 = rho * (p1.sum() - p1)
+    lam = lam + t2.astype(np.float32)
+    p2 = t2 / (1 - rho)
+    lam = lam + (rho * (p2.sum() - p2)).astype(np.float32)
+    assert np.allclose(g[:4], lam, rtol=0, atol=1e-7) and np.allclose(h[:4], 0.25 * 0.75, atol=1e-7)
+    assert g[4] == 0 and h[4] == 0                           # a query of one document has no gradient
+    assert abs(g[:4].sum()) < 1e-6                           # the first-order terms of a query cancel
