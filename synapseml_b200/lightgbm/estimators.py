@@ -254,7 +254,7 @@ class LightGBMBase:
             return self._train_one_data_batch(df)
         # dataset.randomSplit(equal weights): every row draws its batch (Spark's split is seeded at random; here by `seed`)
         rng = np.random.Generator(np.random.PCG64(self._p["seed"] if self._p["seed"] is not None else 0))
-        draws = [rng.integers(0, nb, len(p["label"])) for p in df.partitions]
+        draws = [rng.integers(0, nb, len(p[self._p["labelCol"]])) for p in df.partitions]
         saved = self._p["modelString"]
         model = None
         self.batch_performance_measures = []
@@ -269,9 +269,36 @@ class LightGBMBase:
             self._p["modelString"] = saved
         return model
 
+    def _named_columns(self, df):
+        """The column-name params (labelCol, featuresCol, weightCol, initScoreCol, groupCol — LightGBMParams / Spark's HasLabelCol ...)
+        pick the columns of the frame; the partition tasks below work on the fixed keys "label", "features", "weight", "initScore",
+        "group".  A weight / init-score column is used when its param names it — or, as before, when the frame simply carries a
+        column of the fixed name."""
+        g = self._p
+        names = {"label": g["labelCol"], "features": g["featuresCol"]}
+        if g.get("weightCol"):
+            names["weight"] = g["weightCol"]
+        if g.get("initScoreCol"):
+            names["initScore"] = g["initScoreCol"]
+        if g.get("groupCol"):
+            names["group"] = g["groupCol"]
+        if all(k == v for k, v in names.items()):
+            return df
+        parts = []
+        for p in df.partitions:
+            q = dict(p)
+            for key, col in names.items():
+                if col != key:
+                    if col not in p:
+                        raise KeyError("column %r (%sCol) is not in the data" % (col, key))
+                    q[key] = p[col]
+            parts.append(q)
+        return LocalDataFrame(parts)
+
     def _train_one_data_batch(self, df):
         """trainOneDataBatch: row statistics, bin sample -> reference dataset, then the partition task."""
         import time
+        df = self._named_columns(df)
         import torch.distributed as dist
         g = self._p
         t_start = time.time()
