@@ -102,3 +102,39 @@ def test_ranker_sorts_within_partitions_and_rejects_bad_group_column():
     bad = LocalDataFrame([{"features": np.zeros((2, 2)), "label": np.zeros(2), "group": np.array([0.5, 1.5])}])
     with pytest.raises(ValueError):
         LightGBMRanker().preprocess_data(bad)
+
+
+def test_round_two_params_reach_the_native_string():
+    """CategoricalParams, DartModeParams, SeedParams, monotone constraints and the categorical slot resolution
+    (LightGBMBase.scala:167-198, params/TrainParams.scala)."""
+    c = LightGBMClassifier(boostingType="dart", dropRate=0.2, maxDrop=7, skipDrop=0.3, uniformDrop=True, xGBoostDartMode=True, dropSeed=11,
+                           featureFractionSeed=5, extraSeed=6, baggingSeed=9, categoricalSlotIndexes=[4], categoricalSlotNames=["b", "a"],
+                           slotNames=["a", "b", "c", "d", "e"], minDataPerGroup=50, maxCatThreshold=8, catl2=2.0, catSmooth=5.0, maxCatToOnehot=6,
+                           monotoneConstraints=[1, 0, -1, 0, 0], monotoneConstraintsMethod="basic", monotonePenalty=0.5, maxBinByFeature=[3, 4, 5, 6, 7])
+    assert c.get_categorical_indexes() == [4, 1, 0]
+    s = c.get_train_params(1, 2).to_string()
+    for frag in ("boosting_type=dart", "drop_rate=0.2", "max_drop=7", "skip_drop=0.3", "uniform_drop=true", "xgboost_dart_mode=true", "drop_seed=11",
+                 "feature_fraction_seed=5", "extra_seed=6", "bagging_seed=9", "categorical_feature=4,1,0", "min_data_per_group=50",
+                 "max_cat_threshold=8", "cat_l2=2.0", "cat_smooth=5.0", "max_cat_to_onehot=6", "monotone_constraints=1,0,-1,0,0",
+                 "monotone_constraints_method=basic", "monotone_penalty=0.5", "max_bin_by_feature=3,4,5,6,7"):
+        assert frag in s.split(), (frag, s)
+    plain = LightGBMClassifier(dropRate=0.2, dropSeed=11, featureFractionByNode=0.5).get_train_params(1, 1).to_string()
+    assert "drop_rate" not in plain and "drop_seed" not in plain              # DART parameters only travel with boosting_type=dart
+    assert "feature_fraction_bynode" not in plain                             # declared by the reference, never written (BaseTrainParams.scala)
+    r = LightGBMRanker(objective="rank_xendcg", objectiveSeed=3).get_train_params(1, 1).to_string()
+    assert "objective=rank_xendcg" in r and "objective_seed=3" in r
+    assert "objective_seed" not in LightGBMRanker(objectiveSeed=3).get_train_params(1, 1).to_string()
+    with pytest.raises(ValueError):
+        LightGBMClassifier(categoricalSlotNames=["a"]).get_categorical_indexes()      # names need slotNames
+
+
+def test_column_name_params_pick_the_columns():
+    X, y, w = np.zeros((6, 2)), np.arange(6.0), np.ones(6)
+    df = LocalDataFrame([{"x": X, "target": y, "wt": w, "base": y * 0.1}])
+    est = LightGBMRegressor(labelCol="target", featuresCol="x", weightCol="wt", initScoreCol="base")
+    p = est._named_columns(df).partitions[0]
+    assert p["label"] is y and p["features"] is X and p["weight"] is w and np.array_equal(p["initScore"], y * 0.1)
+    with pytest.raises(KeyError):
+        LightGBMRegressor(weightCol="nope")._named_columns(LocalDataFrame([{"features": X, "label": y}]))
+    same = LocalDataFrame([{"features": X, "label": y}])
+    assert LightGBMRegressor()._named_columns(same) is same

@@ -93,3 +93,78 @@ def test_dump_model_json_describes_the_same_trees(native):
     block = text.split("feature_importances:\n")[1].split("\n\n")[0].strip().splitlines()
     assert {k: int(v) for k, v in doc["feature_importances"].items()} == {l.split("=")[0]: int(l.split("=")[1]) for l in block}
     lb.free_native_memory()
+
+
+CAT_MODEL = """tree
+version=v3
+num_class=1
+num_tree_per_iteration=1
+label_index=0
+max_feature_idx=1
+objective=regression
+feature_names=Column_0 Column_1
+feature_infos=-1:2:0:35 [0:1]
+tree_sizes=1
+
+Tree=0
+num_leaves=3
+num_cat=1
+split_feature=0 1
+split_gain=10 2
+threshold=0 0.5
+decision_type=1 2
+left_child=1 -1
+right_child=-2 -3
+leaf_value=1 2 3
+leaf_weight=5 5 10
+leaf_count=5 5 10
+internal_value=0 0
+internal_weight=20 10
+internal_count=20 10
+cat_boundaries=0 2
+cat_threshold=5 8
+is_linear=0
+shrinkage=1
+
+
+end of trees
+
+feature_importances:
+Column_0=1
+Column_1=1
+
+parameters:
+[objective: regression]
+end of parameters
+
+pandas_categorical:null
+"""
+
+
+def test_categorical_model_text_round_trip_and_dump(native):
+    """A model with a categorical split (Tree::SplitCategorical layout: num_cat, decision_type bit 0, cat_boundaries, cat_threshold
+    bitsets over the category values) is parsed, written back unchanged and dumped as upstream's JSON ("==", categories joined by
+    "||") — all on the host."""
+    import json
+    h, it = C.c_void_p(), C.c_int()
+    assert native.LGBM_BoosterLoadModelFromString(CAT_MODEL.encode(), C.byref(it), C.byref(h)) == 0, native.LGBM_GetLastError()
+    once = _save(native, h)
+    for frag in ("num_cat=1", "decision_type=1 2", "cat_boundaries=0 2", "cat_threshold=5 8", "feature_infos=-1:2:0:35 [0:1]"):
+        assert frag in once, frag
+    size = 1 << 20
+    buf, n = C.create_string_buffer(size), C.c_int64()
+    assert native.LGBM_BoosterDumpModel(h, 0, -1, 0, C.c_int64(size), C.byref(n), buf) == 0
+    dump = json.loads(buf.value.decode())
+    root = dump["tree_info"][0]["tree_structure"]
+    # words 5 (bits 0, 2) and 8 (bit 3 -> category 35): the categories that go left
+    assert root["decision_type"] == "==" and root["threshold"] == "0||2||35" and dump["tree_info"][0]["num_cat"] == 1
+    assert root["left_child"]["decision_type"] == "<=" and root["right_child"]["leaf_index"] == 1
+    assert dump["feature_infos"]["Column_0"] == {"min_value": -1, "max_value": 35, "values": [-1, 2, 0, 35]}
+    assert native.LGBM_BoosterFree(h) == 0
+    h2 = C.c_void_p()
+    assert native.LGBM_BoosterLoadModelFromString(once.encode(), C.byref(it), C.byref(h2)) == 0
+    assert _save(native, h2) == once
+    assert native.LGBM_BoosterFree(h2) == 0
+    # a categorical node that points outside the tree's category sets is refused
+    bad = CAT_MODEL.replace("threshold=0 0.5", "threshold=3 0.5")
+    assert native.LGBM_BoosterLoadModelFromString(bad.encode(), C.byref(it), C.byref(h2)) == -1
