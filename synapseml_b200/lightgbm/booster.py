@@ -50,15 +50,64 @@ class LightGBMBooster:
         out = out[:out_len.value]
         return out.reshape(n, -1) if predict_type in (self.PREDICT_LEAF, self.PREDICT_CONTRIB) else out
 
-    def score(self, row, raw=False):
-        """score (:407-427 -> predictForMat :520-557): one row through LGBM_BoosterPredictForMatSingleRow."""
+    def score(self, row, raw=False, classification=None, disable_shape_check=False):
+        """score (:394-405 -> predictForMat :520-557): one row through LGBM_BoosterPredictForMatSingleRow.  Without `classification`
+        the single native value; with it the reference's array — one value per class, a binary model's single value expanded to
+        [-raw, raw] or [1 - p, p] (predScoreToArray :559-575)."""
         lib = lightgbmlib()
         x = np.ascontiguousarray(row, dtype=np.float64).reshape(-1)
-        out, out_len = np.zeros(1), C.c_int64()
+        k = self.num_classes()
+        out, out_len = np.zeros(k), C.c_int64()
         validate(lib.LGBM_BoosterPredictForMatSingleRow(self.booster_handle, x.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int(len(x)), C.c_int(1),
-                                                        C.c_int(self.PREDICT_RAW if raw else self.PREDICT_NORMAL), C.c_int(0), C.c_int(-1), b"",
+                                                        C.c_int(self.PREDICT_RAW if raw else self.PREDICT_NORMAL), C.c_int(self.start_iteration),
+                                                        C.c_int(self.num_iterations_predict),
+                                                        ("max_bin=255 predict_disable_shape_check=%s" % ("true" if disable_shape_check else "false")).encode(),
                                                         C.byref(out_len), out.ctypes.data_as(C.POINTER(C.c_double))), "Booster Predict")
-        return float(out[0])
+        if classification is None:
+            return float(out[0])
+        if classification and k == 1:
+            return [-out[0], out[0]] if raw else [1 - out[0], out[0]]
+        return out.tolist()
+
+    def predict_leaf(self, row):
+        """predictLeaf (:407-416): the leaf index of one row in every tree."""
+        return self.predict_for_mat(row, self.PREDICT_LEAF, self.start_iteration, self.num_iterations_predict)[0].tolist()
+
+    def features_shap(self, row):
+        """featuresShap (:418-427): (numFeatures + 1) values per class — the TreeSHAP contributions and the expected value."""
+        return self.predict_for_mat(row, self.PREDICT_CONTRIB, self.start_iteration, self.num_iterations_predict)[0].tolist()
+
+    # prediction window (:433-451): first iteration used and how many (<= 0: all of them from the start iteration on)
+    start_iteration, num_iterations_predict, best_iteration = 0, -1, -1
+
+    def set_start_iteration(self, start_iteration):
+        self.start_iteration = int(start_iteration)
+
+    def set_num_iterations(self, num_iterations):
+        self.num_iterations_predict = int(num_iterations)
+
+    def set_best_iteration(self, best_iteration):
+        self.best_iteration = int(best_iteration)
+        self.num_iterations_predict = int(best_iteration)
+
+    def get_native_model(self):
+        """getNativeModel (:471-473)."""
+        return self.model_str if self.model_str is not None else self.save_to_string()
+
+    def save_native_model(self, filename, overwrite=True):
+        """saveNativeModel (:458-468): the model text as a file; an existing file is an error unless overwrite."""
+        if not filename:
+            raise ValueError("filename should not be empty or null.")
+        with open(filename, "w" if overwrite else "x") as f:
+            f.write(self.get_native_model())
+
+    def num_model_per_iteration(self):
+        out = C.c_int()
+        validate(lightgbmlib().LGBM_BoosterNumModelPerIteration(self.booster_handle, C.byref(out)), "Booster models per iteration")
+        return out.value
+
+    def num_total_iterations(self):
+        return self.num_total_model() // self.num_model_per_iteration()      # :518
 
     def update_one_iteration(self):
         fin = C.c_int()

@@ -82,6 +82,9 @@ _DEFAULTS = dict(
     numBatches=0,
     # model output columns (LightGBMPredictionParams): empty = not produced; startIteration: first iteration used for prediction
     leafPredictionCol="", featuresShapCol="", startIteration=0, predictDisableShapeCheck=False,
+    # Spark's predictor columns: an empty name leaves the column out of transform's result (LightGBMClassifier.scala:129-146);
+    # thresholds (ProbabilisticClassificationModel): one per class, the predicted class maximises probability / threshold
+    predictionCol="prediction", rawPredictionCol="rawPrediction", probabilityCol="probability", thresholds=None,
     maxNumClasses=100,      # LightGBMClassifier: more label values than this is taken for a regression problem and refused
     # Spark-only controls, accepted and without effect here (one process per GPU, launched by torchrun: no Spark tasks to cap,
     # barrier or repartition, no driver socket)
@@ -365,9 +368,14 @@ class LightGBMBase:
             model_str = payload[0]
         model = self._make_model(model_str)
         model.best_iteration = self.best_iteration
+        # getModel(...).setNumIterations(lightGBMBooster.bestIteration) (LightGBMClassifier.scala:80): after early stopping the model
+        # predicts with bestIteration iterations — the 0-based index, i.e. one tree set fewer than saveToString kept; -1 otherwise
+        model.numIterations = -1 if self.best_iteration is None else int(self.best_iteration)
         model.leafPredictionCol, model.featuresShapCol = g["leafPredictionCol"], g["featuresShapCol"]
         model.startIteration = g["startIteration"]
         model.predictDisableShapeCheck = bool(g["predictDisableShapeCheck"])
+        model.predictionCol, model.rawPredictionCol, model.probabilityCol = g["predictionCol"], g["rawPredictionCol"], g["probabilityCol"]
+        model.thresholds = None if g["thresholds"] is None else [float(t) for t in g["thresholds"]]
         return model
 
     def add_custom_train_params(self, train_params, df, dist):
@@ -392,6 +400,20 @@ class LightGBMModelBase:
         # LightGBMPredictionParams: optional output columns of transform, and the first iteration used for prediction
         self.leafPredictionCol, self.featuresShapCol, self.startIteration = "", "", 0
         self.predictDisableShapeCheck = False
+        self.predictionCol, self.rawPredictionCol, self.probabilityCol, self.thresholds = "prediction", "rawPrediction", "probability", None
+        self.numIterations = -1      # LightGBMPredictionParams.numIterations: iterations used for prediction, <= 0 = all from startIteration
+
+    def setNumIterations(self, v):
+        self.numIterations = int(v)
+        return self
+
+    def setPredictionCol(self, v):
+        self.predictionCol = v
+        return self
+
+    def getLightGBMBooster(self):
+        """LightGBMModelParams.getLightGBMBooster: the booster wrapper the model scores with."""
+        return self._native()
 
     def setLeafPredictionCol(self, v):
         self.leafPredictionCol = v
@@ -414,7 +436,8 @@ class LightGBMModelBase:
         return out
 
     def _predict(self, features, predict_type):
-        return self._native().predict_for_mat(features, predict_type, start_iteration=self.startIteration,
+        # updateBoosterParamsBeforePredict (LightGBMModelMethods.scala:129-132): the model's startIteration / numIterations go to the booster
+        return self._native().predict_for_mat(features, predict_type, start_iteration=self.startIteration, num_iteration=self.numIterations,
                                               disable_shape_check=self.predictDisableShapeCheck)
 
     def setPredictDisableShapeCheck(self, v):
@@ -499,27 +522,65 @@ class LightGBMModelBase:
 
 
 class LightGBMClassificationModel(LightGBMModelBase):
+    def setRawPredictionCol(self, v):
+        self.rawPredictionCol = v
+        return self
+
+    def setProbabilityCol(self, v):
+        self.probabilityCol = v
+        return self
+
+    def setThresholds(self, v):
+        self.thresholds = None if v is None else [float(t) for t in v]
+        return self
+
+    def getActualNumClasses(self):
+        """HasActualNumClasses (LightGBMClassifier.scala:93-98, 202): the booster's class count — 2 for a binary model."""
+        K = self._model.num_tree_per_iteration
+        return K if K > 1 else 2
+
+    @property
+    def numClasses(self):
+        return self.getActualNumClasses()
+
     def transform(self, features):
+        """LightGBMClassificationModel.transform (LightGBMClassifier.scala:118-163): raw scores and probabilities come from the native
+        predictor; the prediction is the arg max of the raw scores, or — with thresholds — of probability / threshold (Spark's
+        probability2prediction: a class with threshold 0 wins unless its probability is 0 too).  Columns with an empty name are left out."""
+        K = self._model.num_tree_per_iteration
+        if self.thresholds is not None and len(self.thresholds) != self.numClasses:
+            raise ValueError("LightGBMClassificationModel.transform() called with non-matching numClasses and thresholds.length. numClasses=%d, "
+                             "but thresholds has length %d" % (self.numClasses, len(self.thresholds)))
         raw = self.predict_raw(features)
         p = self._predict(features, LightGBMBooster.PREDICT_NORMAL)
-        K = self._model.num_tree_per_iteration
-        if K > 1:      # multiclass: one raw score / probability per class (LightGBMBooster.scala:559-575), prediction = arg max
-            return self._extra_columns(features, dict(rawPrediction=raw, probability=p.reshape(-1, K), prediction=np.argmax(raw, axis=1).astype(np.float64)))
         # binary: the native value is the positive-class score; expanded as the reference does (LightGBMBooster.scala:559-575)
-        return self._extra_columns(features, dict(rawPrediction=np.stack([-raw, raw], axis=1), probability=np.stack([1 - p, p], axis=1),
-                                                  prediction=(p > 0.5).astype(np.float64)))
+        raw2 = raw if K > 1 else np.stack([-raw, raw], axis=1)
+        prob2 = p.reshape(-1, K) if K > 1 else np.stack([1 - p, p], axis=1)
+        out = {}
+        if self.rawPredictionCol:
+            out[self.rawPredictionCol] = raw2
+        if self.probabilityCol:
+            out[self.probabilityCol] = prob2
+        if self.predictionCol:
+            if self.thresholds is None:
+                out[self.predictionCol] = np.argmax(raw2, axis=1).astype(np.float64)
+            else:
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    scaled = prob2 / np.asarray(self.thresholds, dtype=np.float64)[None, :]
+                out[self.predictionCol] = np.argmax(np.where(np.isnan(scaled), -np.inf, scaled), axis=1).astype(np.float64)
+        return self._extra_columns(features, out)
 
 
 class LightGBMRegressionModel(LightGBMModelBase):
     def transform(self, features):
         # LightGBMRegressionModel.predict: score(features, raw = false): the objective's output transform applies (exp for
         # poisson / gamma / tweedie, identity otherwise)
-        return self._extra_columns(features, dict(prediction=self._predict(features, LightGBMBooster.PREDICT_NORMAL)))
+        return self._extra_columns(features, {self.predictionCol: self._predict(features, LightGBMBooster.PREDICT_NORMAL)} if self.predictionCol else {})
 
 
 class LightGBMRankerModel(LightGBMModelBase):
     def transform(self, features):
-        return self._extra_columns(features, dict(prediction=self.predict_raw(features)))
+        return self._extra_columns(features, {self.predictionCol: self.predict_raw(features)} if self.predictionCol else {})
 
 
 class LightGBMClassifier(LightGBMBase):

@@ -223,3 +223,89 @@ def test_predict_disable_shape_check(native):
     narrow = X[:200, :20]
     padded = np.concatenate([narrow, np.zeros((200, 8))], axis=1)
     assert np.array_equal(model.predict_raw(narrow), model.predict_raw(padded))
+
+
+def test_prediction_columns_and_thresholds(native):
+    # Spark's predictor columns on the classification model (LightGBMClassifier.scala:118-163): renamed columns, a column left out by
+    # an empty name, thresholds re-weighting the predicted class (ProbabilisticClassificationModel.probability2prediction)
+    X, y = S.higgs_shape(20000)
+    df = LocalDataFrame.from_arrays(X, y, num_partitions=1)
+    model = LightGBMClassifier(numIterations=8, numLeaves=15, predictionCol="pred", rawPredictionCol="", probabilityCol="prob").fit(df)
+    out = model.transform(X[:4000])
+    assert set(out) == {"pred", "prob"}
+    p = out["prob"][:, 1]
+    assert np.array_equal(out["pred"], (p > 0.5).astype(np.float64))
+    assert model.getActualNumClasses() == 2 and model.numClasses == 2 and model.getLightGBMBooster().num_classes() == 1
+    model.setThresholds([0.8, 0.2])
+    shifted = model.transform(X[:4000])["pred"]
+    assert np.array_equal(shifted, (p / 0.2 > (1 - p) / 0.8).astype(np.float64)) and shifted.sum() > out["pred"].sum()
+    model.setThresholds([0.0, 1.0])       # a zero threshold always wins (its probability is never exactly 0 here)
+    assert not model.transform(X[:4000])["pred"].any()
+    with pytest.raises(ValueError):
+        model.setThresholds([0.5, 0.3, 0.2]).transform(X[:10])
+    # multiclass, thresholds through the estimator
+    rng = np.random.Generator(np.random.PCG64(3))
+    y3 = np.digitize(X[:, 0] + 0.3 * rng.normal(size=len(X)), [-0.5, 0.6]).astype(np.float64)
+    m3 = LightGBMClassifier(objective="multiclass", numIterations=5, numLeaves=7, thresholds=[1.0, 0.1, 1.0]).fit(LocalDataFrame.from_arrays(X, y3))
+    o3 = m3.transform(X[:3000])
+    assert m3.getActualNumClasses() == 3
+    assert np.array_equal(o3["prediction"], np.argmax(o3["probability"] / np.array([1.0, 0.1, 1.0]), axis=1).astype(np.float64))
+    assert (o3["prediction"] == 1).mean() > (np.argmax(o3["rawPrediction"], axis=1) == 1).mean()
+    # the regressor's only column
+    r = LightGBMRegressor(numIterations=3, numLeaves=7, predictionCol="yhat").fit(df).transform(X[:100])
+    assert set(r) == {"yhat"}
+
+
+def test_booster_wrapper_methods_and_prediction_window(native, tmp_path):
+    # LightGBMBooster.scala:394-518: score's class expansion, predictLeaf / featuresShap of one row, the start / count window
+    # setStartIteration / setNumIterations / setBestIteration put on every prediction, saveNativeModel, the iteration counts
+    from synapseml_b200.lightgbm.booster import LightGBMBooster
+    X, y = S.higgs_shape(20000)
+    model = LightGBMClassifier(numIterations=6, numLeaves=7).fit(LocalDataFrame.from_arrays(X, y))
+    b = model.getLightGBMBooster()
+    assert b.num_total_iterations() == 6 and b.num_model_per_iteration() == 1 and b.get_native_model() == model.getNativeModel()
+    r, p = b.score(X[5], raw=True), b.score(X[5])
+    assert b.score(X[5], raw=True, classification=True) == [-r, r] and b.score(X[5], classification=True) == [1 - p, p]
+    assert b.score(X[5], raw=True, classification=False) == [r]
+    leaves = b.predict_leaf(X[5])
+    assert len(leaves) == 6 and leaves == model.predict_leaf(X[5:6])[0].tolist()
+    shap = b.features_shap(X[5])
+    assert len(shap) == X.shape[1] + 1 and abs(sum(shap) - r) < 1e-9
+    b.save_native_model(str(tmp_path / "m.txt"))
+    assert open(tmp_path / "m.txt").read() == model.getNativeModel()
+    with pytest.raises(FileExistsError):
+        b.save_native_model(str(tmp_path / "m.txt"), overwrite=False)
+    with pytest.raises(ValueError):
+        b.save_native_model("")
+    # the window: the model's numIterations / startIteration reach the native predictor
+    full = model.predict_raw(X[:500])
+    first2 = model.setNumIterations(2).predict_raw(X[:500])
+    rest = model.setNumIterations(-1).setStartIteration(2).predict_raw(X[:500])
+    model.setStartIteration(0)
+    two = LightGBMBooster(model_str=b.save_to_string(2))
+    assert np.array_equal(first2, two.predict_for_mat(X[:500], LightGBMBooster.PREDICT_RAW))
+    assert np.allclose(first2 + rest, full, rtol=0, atol=1e-12) and not np.array_equal(first2, full)
+    two.set_best_iteration(1)
+    assert two.best_iteration == 1 and len(two.predict_leaf(X[0])) == 1
+    two.free_native_memory()
+
+
+def test_early_stopped_model_predicts_with_best_iteration_trees(native):
+    # getModel(...).setNumIterations(booster.bestIteration) (LightGBMClassifier.scala:80): the model text keeps bestIteration + 1
+    # iterations (saveToString, LightGBMBooster.scala:272-278) and transform uses the first bestIteration of them
+    X, y = S.higgs_shape(30000)
+    rng = np.random.Generator(np.random.PCG64(9))
+    y = np.where(rng.random(len(y)) < 0.35, 1 - y, y).astype(np.float32)
+    valid = np.zeros(len(y), dtype=bool)
+    valid[20000:] = True
+    est = LightGBMClassifier(numIterations=100, numLeaves=63, learningRate=0.3, minDataInLeaf=5, validationIndicatorCol="isVal",
+                             earlyStoppingRound=3, metric="binary_logloss", samplingMode="fixed")
+    model = est.fit(LocalDataFrame.from_arrays(X, y, num_partitions=2, isVal=valid))
+    best = est.best_iteration
+    assert best is not None and best >= 1 and model.getBoosterBestIteration() == best and model.numIterations == best
+    assert model.getBoosterNumTotalIterations() == best + 1
+    from synapseml_b200.lightgbm.booster import LightGBMBooster
+    lb = LightGBMBooster(model_str=model.getNativeModel())
+    assert np.array_equal(model.predict_raw(X[:300]), lb.predict_for_mat(X[:300], LightGBMBooster.PREDICT_RAW, num_iteration=best))
+    assert model.predict_leaf(X[:5]).shape == (5, best)
+    lb.free_native_memory()
