@@ -298,7 +298,7 @@ def test_early_stopped_model_predicts_with_best_iteration_trees(native):
     y = np.where(rng.random(len(y)) < 0.35, 1 - y, y).astype(np.float32)
     valid = np.zeros(len(y), dtype=bool)
     valid[20000:] = True
-    est = LightGBMClassifier(numIterations=100, numLeaves=63, learningRate=0.3, minDataInLeaf=5, validationIndicatorCol="isVal",
+    est = LightGBMClassifier(numIterations=300, numLeaves=15, learningRate=0.1, validationIndicatorCol="isVal",
                              earlyStoppingRound=3, metric="binary_logloss", samplingMode="fixed")
     model = est.fit(LocalDataFrame.from_arrays(X, y, num_partitions=2, isVal=valid))
     best = est.best_iteration
