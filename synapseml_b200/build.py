@@ -51,7 +51,7 @@ def build(force=False, verbose=False):
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    subprocess.check_call([NVCC, "-shared", "-cudart", "static", "-ccbin", "/usr/bin/g++", "-o", OUT] + objs + ["-ldl", "-lpthread", "-Xlinker", "--no-undefined"])
+    subprocess.check_call([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-ccbin", "/usr/bin/g++", "-o", OUT] + objs + ["-ldl", "-lpthread", "-Xlinker", "--no-undefined"])
     return OUT
 
 

@@ -113,3 +113,31 @@ def test_world_size_2_rendezvous_and_unique_id_handoff(native, tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=180)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert (tmp_path / "rank0.ok").exists() and (tmp_path / "rank1.ok").exists()
+
+
+def test_hot_kernels_are_built_for_sm_100a_without_spills(native):
+    """Build evidence that needs no GPU: the library carries sm_100a code only, and the kernels of the boosting loop's hot path keep
+    their working set in registers — no local-memory frame on the histogram kernels' main variants or on the plain split-search
+    kernel (the categorical / wide / constrained search is compiled into its own instantiation so that it costs the plain one nothing)."""
+    import shutil
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    lib = os.path.join(ROOT, "synapseml_b200", "lib", "lib_lightgbm.so")
+    out = subprocess.run([cuobjdump, "--dump-resource-usage", lib], capture_output=True, text=True, check=True).stdout
+    archs = set(re.findall(r"arch = (sm_\w+)", out))
+    assert archs == {"sm_100a"}, archs
+    usage = {}
+    lines = out.splitlines()
+    for i, line in enumerate(lines):
+        m = re.match(r"\s*Function (\S+):", line)
+        if m and i + 1 < len(lines):
+            usage[m.group(1)] = {k: int(v) for k, v in re.findall(r"(REG|STACK|SHARED|LOCAL):(\d+)", lines[i + 1])}
+    find_plain = [u for n, u in usage.items() if re.match(r"_ZN3lgb9k_bt_findILb[01]ELb0EEE", n)]
+    find_ext = [u for n, u in usage.items() if re.match(r"_ZN3lgb9k_bt_findILb[01]ELb1EEE", n)]
+    hist = [u for n, u in usage.items() if n.startswith("_ZN3lgb9k_bt_histI")]
+    assert len(find_plain) == 2 and len(find_ext) == 2 and len(hist) >= 12
+    assert all(u["STACK"] == 0 and u["LOCAL"] == 0 for u in find_plain), find_plain
+    assert all(u["SHARED"] < min(e["SHARED"] for e in find_ext) for u in find_plain)
+    assert all(u["REG"] <= 64 and u["LOCAL"] == 0 and u["STACK"] <= 32 for u in hist), hist      # 1024 threads per CTA need <= 64 registers
+    assert all(u["LOCAL"] == 0 for u in usage.values())
