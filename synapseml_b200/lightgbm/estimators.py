@@ -562,13 +562,18 @@ class LightGBMClassificationModel(LightGBMModelBase):
         if self.probabilityCol:
             out[self.probabilityCol] = prob2
         if self.predictionCol:
-            if self.thresholds is None:
-                out[self.predictionCol] = np.argmax(raw2, axis=1).astype(np.float64)
-            else:
-                with np.errstate(divide="ignore", invalid="ignore"):
-                    scaled = prob2 / np.asarray(self.thresholds, dtype=np.float64)[None, :]
-                out[self.predictionCol] = np.argmax(np.where(np.isnan(scaled), -np.inf, scaled), axis=1).astype(np.float64)
+            out[self.predictionCol] = (np.argmax(raw2, axis=1).astype(np.float64) if self.thresholds is None
+                                       else self.probability_to_prediction(prob2, self.thresholds))
         return self._extra_columns(features, out)
+
+    @staticmethod
+    def probability_to_prediction(probability, thresholds):
+        """Spark's ProbabilisticClassificationModel.probability2prediction with thresholds: the first class that maximises
+        probability / threshold.  A zero threshold scales to +inf and wins — unless its probability is 0 as well (0 / 0 is NaN, which
+        never compares greater); with nothing greater than -inf the answer stays class 0."""
+        with np.errstate(divide="ignore", invalid="ignore"):
+            scaled = np.asarray(probability, dtype=np.float64) / np.asarray(thresholds, dtype=np.float64)[None, :]
+        return np.argmax(np.where(np.isnan(scaled), -np.inf, scaled), axis=1).astype(np.float64)
 
 
 class LightGBMRegressionModel(LightGBMModelBase):

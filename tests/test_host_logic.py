@@ -138,3 +138,18 @@ def test_column_name_params_pick_the_columns():
         LightGBMRegressor(weightCol="nope")._named_columns(LocalDataFrame([{"features": X, "label": y}]))
     same = LocalDataFrame([{"features": X, "label": y}])
     assert LightGBMRegressor()._named_columns(same) is same
+
+
+def test_thresholds_pick_the_class_as_spark_does():
+    # ProbabilisticClassificationModel.probability2prediction: arg max of probability / threshold, first maximum wins, a zero threshold
+    # always wins unless its probability is zero too
+    from synapseml_b200.lightgbm.estimators import LightGBMClassificationModel
+    f = LightGBMClassificationModel.probability_to_prediction
+    p = np.array([[0.6, 0.4], [0.3, 0.7], [0.5, 0.5]])
+    assert f(p, [0.5, 0.5]).tolist() == [0.0, 1.0, 0.0]                       # a tie keeps the first class
+    assert f(p, [0.9, 0.1]).tolist() == [1.0, 1.0, 1.0]
+    assert f(p, [0.0, 1.0]).tolist() == [0.0, 0.0, 0.0]                       # +inf wins
+    assert f(np.array([[0.0, 1.0], [0.2, 0.8]]), [0.0, 1.0]).tolist() == [1.0, 0.0]      # 0 / 0 never wins
+    p3 = np.array([[0.2, 0.3, 0.5], [0.1, 0.1, 0.8]])
+    assert f(p3, [0.1, 0.6, 1.0]).tolist() == [0.0, 0.0] and f(p3, [1.0, 1.0, 1.0]).tolist() == [2.0, 2.0]
+    assert f(np.zeros((1, 3)), [0.0, 0.0, 0.0]).tolist() == [0.0]             # nothing compares greater: class 0
