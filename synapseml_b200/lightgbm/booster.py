@@ -159,7 +159,8 @@ class LightGBMBooster:
         """saveToString: LGBM_BoosterSaveModelToString with grow-and-retry (what the SWIG wrapper does)."""
         lib = lightgbmlib()
         n_iter = -1 if upper_iteration is None else int(upper_iteration)
-        size = 1 << 20
+        # first guess: ~4 KB per 31-leaf tree, so that the usual model is written once and not generated a second time for the retry
+        size = max(1 << 20, self.num_total_model() * 4096 + (1 << 16))
         while True:
             buf = C.create_string_buffer(size)
             out_len = C.c_int64()
