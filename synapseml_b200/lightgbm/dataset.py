@@ -67,30 +67,37 @@ class SampledData:
             self.row_counts[col] = k + 1
 
     def push_rows(self, rows, block=None):
-        """Equivalent of calling push_row for rows 0..n-1 in order, done in cache-sized row blocks: a block without zeros goes into all
-        columns with one transposed copy, otherwise column by column."""
+        """Equivalent of calling push_row for rows 0..n-1 in order, done in cache-sized row blocks: a block is transposed once, then a
+        column without zeros is one contiguous copy and a column with zeros a gather of its non-zero positions."""
         rows = np.asarray(rows, dtype=np.float64)
         n = rows.shape[0]
         base = self._next_row
-        if block is None:      # ~16 MB of doubles per block
-            block = int(min(65536, max(128, (1 << 21) // max(self.num_cols, 1))))
+        if block is None:      # ~2 MB of doubles per block (the transposed block stays in cache while its columns are copied), but
+            block = int(min(65536, max(4096, (1 << 18) // max(self.num_cols, 1))))      # never so few rows that the per-column Python loop dominates on wide data
         for b in range(0, n, block):
             blk = rows[b:b + block]
             nb = blk.shape[0]
-            nzmask = blk != 0.0
             k0 = int(self.row_counts[0]) if self.num_cols else 0
-            if nzmask.all() and (self.row_counts == k0).all():
+            if (self.row_counts == k0).all() and (blk != 0.0).all():      # dense data: all columns with one transposed copy
                 self._data[:, k0:k0 + nb] = blk.T
                 self._idx[:, k0:k0 + nb] = np.arange(base + b, base + b + nb, dtype=np.int32)
                 self.row_counts += nb
                 continue
             blk_t = np.ascontiguousarray(blk.T)
-            mask_t = np.ascontiguousarray(nzmask.T)
+            full = (blk_t != 0.0).all(axis=1)
+            index = None
             for col in range(self.num_cols):
-                nz = np.flatnonzero(mask_t[col])
+                k = int(self.row_counts[col])
+                if full[col]:
+                    if index is None:
+                        index = np.arange(base + b, base + b + nb, dtype=np.int32)
+                    self._data[col, k:k + nb] = blk_t[col]
+                    self._idx[col, k:k + nb] = index
+                    self.row_counts[col] = k + nb
+                    continue
+                nz = np.flatnonzero(blk_t[col])      # NaN counts as non-zero, -0.0 as zero: as `!= 0.0` does
                 if len(nz) == 0:
                     continue
-                k = int(self.row_counts[col])
                 self._data[col, k:k + len(nz)] = blk_t[col, nz]
                 self._idx[col, k:k + len(nz)] = nz + (base + b)
                 self.row_counts[col] = k + len(nz)

@@ -62,6 +62,28 @@ def test_sampled_data_layout():
         assert np.array_equal(sd.sample_indexes[j][:k], sd2.sample_indexes[j][:k])
 
 
+def test_sampled_data_blocks_equal_row_by_row_pushes():
+    # push_rows over several blocks and calls: columns without zeros, with zeros, all zero, with NaN and -0.0
+    rng = np.random.Generator(np.random.PCG64(4))
+    rows = rng.normal(size=(700, 6))
+    rows[:, 1] = np.where(rng.random(700) < 0.5, 0.0, rows[:, 1])
+    rows[:, 2] = 0.0
+    rows[rng.random(700) < 0.1, 3] = np.nan
+    rows[rng.random(700) < 0.3, 4] = -0.0
+    rows[300:, 5] = np.where(rng.random(400) < 0.2, 0.0, rows[300:, 5])      # full in the first blocks only
+    one = SampledData(700, 6)
+    for i, r in enumerate(rows):
+        one.push_row(r, i)
+    blocks = SampledData(700, 6)
+    blocks.push_rows(rows[:450], block=128)
+    blocks.push_rows(rows[450:], block=100)
+    assert one.row_counts.tolist() == blocks.row_counts.tolist() and one.row_counts[2] == 0 and one.row_counts[0] == 700
+    for j in range(6):
+        k = one.row_counts[j]
+        assert np.array_equal(one.sample_data[j][:k], blocks.sample_data[j][:k], equal_nan=True)
+        assert np.array_equal(one.sample_indexes[j][:k], blocks.sample_indexes[j][:k])
+
+
 def test_group_id_manager():
     g = GroupIdManager()
     assert [g.get_unique_index_for_id(v) for v in ["q7", "q7", "q2", "q7", 5]] == [0, 0, 1, 0, 2]
