@@ -6,6 +6,8 @@ Mirrors LightGBMBase.scala (train :36-65, trainOneDataBatch :396-447, calculateR
 LightGBMRanker.scala:26-121.  One process is one executor with one GPU; under torchrun every rank calls fit() with its
 own partitions (rows of rank r precede rows of rank r+1 in the global order).
 """
+import re
+
 import numpy as np
 
 from . import network_manager as nm
@@ -395,7 +397,11 @@ class LightGBMModelBase:
 
     def __init__(self, model_str):
         self.model_str = model_str
-        self._model = TextModel(model_str)       # parsed text: feature importances only
+        self._parsed = None                       # the text parsed in Python, on first use (tests and tools; scoring is native)
+        m = re.search(r"^num_tree_per_iteration=(\d+)", model_str, flags=re.M)
+        if m is None:
+            raise ValueError("Model string has no num_tree_per_iteration line")
+        self._trees_per_iteration = int(m.group(1))
         self._booster = None
         # LightGBMPredictionParams: optional output columns of transform, and the first iteration used for prediction
         self.leafPredictionCol, self.featuresShapCol, self.startIteration = "", "", 0
@@ -406,6 +412,12 @@ class LightGBMModelBase:
     def setNumIterations(self, v):
         self.numIterations = int(v)
         return self
+
+    @property
+    def _model(self):
+        if self._parsed is None:
+            self._parsed = TextModel(self.model_str)
+        return self._parsed
 
     def setPredictionCol(self, v):
         self.predictionCol = v
@@ -466,7 +478,7 @@ class LightGBMModelBase:
     def predict_raw(self, features):
         """Raw scores: [n], or [n, num_class] for a multiclass model."""
         raw = self._predict(features, LightGBMBooster.PREDICT_RAW)
-        K = self._model.num_tree_per_iteration
+        K = self._trees_per_iteration
         return raw if K == 1 else raw.reshape(-1, K)
 
     def predict_leaf(self, features):
@@ -502,7 +514,7 @@ class LightGBMModelBase:
         return self._native().num_total_model()
 
     def getBoosterNumTotalIterations(self):
-        return self._native().num_total_model() // max(1, self._model.num_tree_per_iteration)      # LightGBMBooster.scala:518
+        return self._native().num_total_model() // max(1, self._trees_per_iteration)      # LightGBMBooster.scala:518
 
     def getBoosterNumFeatures(self):
         return self._native().num_features()
@@ -536,7 +548,7 @@ class LightGBMClassificationModel(LightGBMModelBase):
 
     def getActualNumClasses(self):
         """HasActualNumClasses (LightGBMClassifier.scala:93-98, 202): the booster's class count — 2 for a binary model."""
-        K = self._model.num_tree_per_iteration
+        K = self._trees_per_iteration
         return K if K > 1 else 2
 
     @property
@@ -547,7 +559,7 @@ class LightGBMClassificationModel(LightGBMModelBase):
         """LightGBMClassificationModel.transform (LightGBMClassifier.scala:118-163): raw scores and probabilities come from the native
         predictor; the prediction is the arg max of the raw scores, or — with thresholds — of probability / threshold (Spark's
         probability2prediction: a class with threshold 0 wins unless its probability is 0 too).  Columns with an empty name are left out."""
-        K = self._model.num_tree_per_iteration
+        K = self._trees_per_iteration
         if self.thresholds is not None and len(self.thresholds) != self.numClasses:
             raise ValueError("LightGBMClassificationModel.transform() called with non-matching numClasses and thresholds.length. numClasses=%d, "
                              "but thresholds has length %d" % (self.numClasses, len(self.thresholds)))
