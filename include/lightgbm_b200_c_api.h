@@ -45,6 +45,12 @@ int LGBM_DatasetCreateFromSampledColumn(double** sample_data, int** sample_indic
                                         int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
                                         const char* parameters, DatasetHandle* out);
 
+/* The same search from the sampled rows as they are — a dense row-major matrix [num_sample_row][ncol] — for callers that hold
+ * the sample that way (LightGBMBase.getSampledRows, LightGBMBase.scala:724-749, collects rows): the zeros are dropped and the
+ * columns gathered on the device, so the host never builds SampledData's per-column arrays.  Same result as the call above. */
+int LGBM_B200_DatasetCreateFromSampledRows(const double* rows, int32_t num_sample_row, int32_t ncol, int32_t num_local_row,
+                                           int64_t num_dist_row, const char* parameters, DatasetHandle* out);
+
 /* dataset/ReferenceDatasetUtils.scala:52-55 — bin mappers as an opaque byte buffer (shipped driver -> executors) */
 int LGBM_DatasetSerializeReferenceToBinary(DatasetHandle handle, ByteBufferHandle* out, int32_t* out_len);
 /* dataset/ReferenceDatasetUtils.scala:107 / :115 */

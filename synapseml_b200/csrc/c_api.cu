@@ -49,6 +49,14 @@ int LGBM_DatasetCreateFromSampledColumn(double** sample_data, int** sample_indic
   API_END();
 }
 
+int LGBM_B200_DatasetCreateFromSampledRows(const double* rows, int32_t num_sample_row, int32_t ncol, int32_t num_local_row,
+                                           int64_t num_dist_row, const char* parameters, DatasetHandle* out) {
+  API_BEGIN();
+  LGB_CHECK(rows != nullptr, "rows must not be null");
+  *out = Dataset::CreateFromSampledColumn(nullptr, nullptr, ncol, nullptr, num_sample_row, num_local_row, num_dist_row, parameters, rows);
+  API_END();
+}
+
 int LGBM_DatasetSerializeReferenceToBinary(DatasetHandle handle, ByteBufferHandle* out, int32_t* out_len) {
   API_BEGIN();
   auto bb = new ByteBuffer();

@@ -62,6 +62,25 @@ __global__ void k1_canon_nan(double* vals, const long long* seg_off, int* na_cnt
   if ((threadIdx.x & 31) == 0 && local) atomicAdd(&na_cnt[f], local);
 }
 
+// A dense row-major sample [rows][nfeat] instead of the host-built column arrays: per column, how many values are not zero (NaN
+// counts, -0.0 does not: SampledData.scala:70-77), then the values themselves into the column's segment.  The order inside a
+// segment is whatever the atomics give; the segments are sorted next, so the result does not depend on it.
+__global__ void k1_dense_count(const double* __restrict__ rows, long long n_elems, int nfeat, int* __restrict__ counts) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_elems; i += (long long)gridDim.x * blockDim.x)
+    if (rows[i] != 0.0) atomicAdd(&counts[static_cast<int>(i % nfeat)], 1);
+}
+
+__global__ void k1_dense_scatter(const double* __restrict__ rows, long long n_elems, int nfeat, const long long* __restrict__ seg_off,
+                                 int* __restrict__ cursor, double* __restrict__ vals) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_elems; i += (long long)gridDim.x * blockDim.x) {
+    const double v = rows[i];
+    if (v != 0.0) {
+      const int f = static_cast<int>(i % nfeat);
+      vals[seg_off[f] + atomicAdd(&cursor[f], 1)] = v;
+    }
+  }
+}
+
 __device__ __forceinline__ double UpperBoundOf(double a) { return nextafter(a, __longlong_as_double(0x7ff0000000000000LL)); }
 __device__ __forceinline__ bool EqualOrdered(double a, double b) { return b <= UpperBoundOf(a); }
 #define K1_ZERO_THRESHOLD ((double)1e-35f)
@@ -815,7 +834,7 @@ void Dataset::AllocateRows(int64_t n) {
 
 Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_indices, int32_t ncol, const int* num_per_col,
                                           int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
-                                          const char* params) {
+                                          const char* params, const double* dense_rows) {
   (void)sample_indices;
   std::unique_ptr<Dataset> ds(new Dataset());
   ds->param_string = params ? params : "";
@@ -833,7 +852,24 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   ds->device = ResolveDevice(c);
   LGB_CUDA(cudaSetDevice(ds->device));
   ds->num_total_features = ncol;
-  // ---- stage the column-major non-zero sample (SampledData.scala:30-40) into one device array
+  // ---- stage the column-major non-zero sample (SampledData.scala:30-40) into one device array; from a dense row-major sample the
+  // device drops the zeros and transposes (the host then never builds the per-column arrays)
+  DevBuf<double> d_rows;
+  std::vector<int> dense_counts;
+  const long long n_elems = static_cast<long long>(num_sample_row) * ncol;
+  const unsigned dense_grid = static_cast<unsigned>(std::max<long long>(1, std::min<long long>(CeilDiv<long long>(n_elems, 256), 148 * 16)));
+  if (dense_rows != nullptr) {
+    LGB_CHECK(num_sample_row > 0, "num_sample_row must be positive");
+    d_rows.Alloc(n_elems);
+    LGB_CUDA(cudaMemcpy(d_rows.p, dense_rows, sizeof(double) * n_elems, cudaMemcpyHostToDevice));
+    DevBuf<int> d_cnt;
+    d_cnt.AllocZero(ncol);
+    k1_dense_count<<<dense_grid, 256>>>(d_rows.p, n_elems, ncol, d_cnt.p);
+    LGB_CUDA(cudaGetLastError());
+    dense_counts.resize(ncol);
+    LGB_CUDA(cudaMemcpy(dense_counts.data(), d_cnt.p, sizeof(int) * ncol, cudaMemcpyDeviceToHost));
+    num_per_col = dense_counts.data();
+  }
   std::vector<long long> off(ncol + 1, 0);
   for (int j = 0; j < ncol; ++j) {
     LGB_CHECK(num_per_col[j] >= 0 && num_per_col[j] <= num_sample_row, "num_per_col[%d]=%d out of range", j, num_per_col[j]);
@@ -846,11 +882,20 @@ Dataset* Dataset::CreateFromSampledColumn(double** sample_data, int** sample_ind
   DevBuf<K1Meta> d_meta;
   d_vals.Alloc(std::max<long long>(total, 1));
   d_sorted.Alloc(std::max<long long>(total, 1));
-  for (int j = 0; j < ncol; ++j)
-    if (num_per_col[j] > 0)
-      LGB_CUDA(cudaMemcpy(d_vals.p + off[j], sample_data[j], sizeof(double) * num_per_col[j], cudaMemcpyHostToDevice));
   d_off.Alloc(ncol + 1);
   LGB_CUDA(cudaMemcpy(d_off.p, off.data(), sizeof(long long) * (ncol + 1), cudaMemcpyHostToDevice));
+  if (dense_rows != nullptr) {
+    DevBuf<int> d_cursor;
+    d_cursor.AllocZero(ncol);
+    k1_dense_scatter<<<dense_grid, 256>>>(d_rows.p, n_elems, ncol, d_off.p, d_cursor.p, d_vals.p);
+    LGB_CUDA(cudaGetLastError());
+    LGB_CUDA(cudaDeviceSynchronize());
+    d_rows.Free();
+  } else {
+    for (int j = 0; j < ncol; ++j)
+      if (num_per_col[j] > 0)
+        LGB_CUDA(cudaMemcpy(d_vals.p + off[j], sample_data[j], sizeof(double) * num_per_col[j], cudaMemcpyHostToDevice));
+  }
   d_na.AllocZero(ncol);
   if (total > 0) {
     dim3 grid(static_cast<unsigned>(std::min<long long>(CeilDiv<long long>(num_sample_row, 256), 64)), ncol);

@@ -116,7 +116,7 @@ class Dataset {
 
   static Dataset* CreateFromSampledColumn(double** sample_data, int** sample_indices, int32_t ncol, const int* num_per_col,
                                           int32_t num_sample_row, int32_t num_local_row, int64_t num_dist_row,
-                                          const char* params);
+                                          const char* params, const double* dense_rows = nullptr);      // dense_rows: the sample as a row-major matrix instead (LGBM_B200_DatasetCreateFromSampledRows)
   static Dataset* CreateFromSerializedReference(const void* buf, int32_t len, int64_t num_row, const char* params);
   Dataset* CreateByReference(int64_t num_row) const;
   std::string SerializeReference() const;

@@ -173,20 +173,29 @@ class LightGBMDataset:
 
 
 class ReferenceDatasetUtils:
+    row_major_sample = True      # False: build SampledData on the host and call LGBM_DatasetCreateFromSampledColumn, as the reference does
+
     @staticmethod
     def create_reference_dataset_from_sample(dataset_params, feature_data_name, num_rows, num_cols, sampled_rows):
         """Driver side (ReferenceDatasetUtils.createReferenceDatasetFromSample, :14-71): sample -> bin mappers -> bytes."""
         del feature_data_name
-        sampled_rows = np.asarray(sampled_rows, dtype=np.float64)
-        sampled = SampledData(len(sampled_rows), num_cols)
-        sampled.push_rows(sampled_rows)
+        sampled_rows = np.ascontiguousarray(sampled_rows, dtype=np.float64)
         lib = lightgbmlib()
         handle = C.c_void_p()
         # num_local_row = 1 and num_dist_row = N, as the reference passes them (:44-45)
-        validate(lib.LGBM_DatasetCreateFromSampledColumn(sampled.get_sample_data(), sampled.get_sample_indices(), C.c_int32(num_cols),
-                                                         sampled.get_row_counts(), C.c_int32(len(sampled_rows)), C.c_int32(1),
-                                                         C.c_int64(num_rows), dataset_params.encode(), C.byref(handle)),
-                 "Dataset create from samples")
+        if ReferenceDatasetUtils.row_major_sample:
+            # the collected rows go to the library as they are; it drops the zeros and gathers the columns on the device
+            validate(lib.LGBM_B200_DatasetCreateFromSampledRows(sampled_rows.ctypes.data_as(C.POINTER(C.c_double)), C.c_int32(len(sampled_rows)),
+                                                                C.c_int32(num_cols), C.c_int32(1), C.c_int64(num_rows),
+                                                                dataset_params.encode(), C.byref(handle)), "Dataset create from samples")
+        else:
+            # the reference's own route: SampledData's column-major non-zero arrays (SampledData.scala:26-96)
+            sampled = SampledData(len(sampled_rows), num_cols)
+            sampled.push_rows(sampled_rows)
+            validate(lib.LGBM_DatasetCreateFromSampledColumn(sampled.get_sample_data(), sampled.get_sample_indices(), C.c_int32(num_cols),
+                                                             sampled.get_row_counts(), C.c_int32(len(sampled_rows)), C.c_int32(1),
+                                                             C.c_int64(num_rows), dataset_params.encode(), C.byref(handle)),
+                     "Dataset create from samples")
         try:
             buf, blen = C.c_void_p(), C.c_int32()
             validate(lib.LGBM_DatasetSerializeReferenceToBinary(handle, C.byref(buf), C.byref(blen)), "Serialize ref")

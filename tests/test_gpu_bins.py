@@ -156,3 +156,23 @@ def assert_same_bins_logical(nd, ods):
     assert nd.num_used() == ods.num_used_feature()
     for j in range(nd.num_used()):
         assert np.array_equal(nd.bin_column(j).astype(np.uint16), ods.bin_column(j)), j
+
+
+@pytest.mark.parametrize("params", ["max_bin=255 min_data_in_leaf=20", "max_bin=15 min_data_in_leaf=5 zero_as_missing=true",
+                                    "max_bin=600 min_data_in_leaf=20 categorical_feature=7,10", "max_bin=63 use_missing=false"])
+def test_row_major_sample_gives_the_reference_of_the_column_arrays(native, params):
+    # LGBM_B200_DatasetCreateFromSampledRows (zeros dropped and columns gathered on the device) against
+    # LGBM_DatasetCreateFromSampledColumn fed with SampledData's host-built arrays: the serialized bin mappers must be the same bytes
+    from synapseml_b200.lightgbm.dataset import ReferenceDatasetUtils
+    for X in (edge_case_matrix(6000, 3), S.higgs_shape(20000)[0], np.zeros((50, 3)), -np.zeros((40, 2)),
+              np.random.Generator(np.random.PCG64(1)).normal(size=(3000, 70))):
+        if "categorical" in params and X.shape[1] < 11:
+            continue
+        out = {}
+        for flag in (True, False):
+            ReferenceDatasetUtils.row_major_sample = flag
+            try:
+                out[flag] = ReferenceDatasetUtils.create_reference_dataset_from_sample(params, "features", 10 * len(X), X.shape[1], X)
+            finally:
+                ReferenceDatasetUtils.row_major_sample = True
+        assert out[True] == out[False] and len(out[True]) > 16, (params, X.shape)
