@@ -183,7 +183,7 @@ class ReferenceDatasetUtils:
         lib = lightgbmlib()
         handle = C.c_void_p()
         # num_local_row = 1 and num_dist_row = N, as the reference passes them (:44-45)
-        if ReferenceDatasetUtils.row_major_sample:
+        if ReferenceDatasetUtils.row_major_sample and len(sampled_rows) > 0:
             # the collected rows go to the library as they are; it drops the zeros and gathers the columns on the device
             validate(lib.LGBM_B200_DatasetCreateFromSampledRows(sampled_rows.ctypes.data_as(C.POINTER(C.c_double)), C.c_int32(len(sampled_rows)),
                                                                 C.c_int32(num_cols), C.c_int32(1), C.c_int64(num_rows),
